@@ -1,0 +1,200 @@
+/*
+ * lgbcu.h -- thin extern "C" CUDA layer of the B200-native histogram tree learner.
+ *
+ * This is the ONLY surface the host C++ (lightgbmv1_b200/csrc/host) calls; host code never includes a CUDA
+ * header.  One function per hot-path step so that each step can be parity-tested alone against the
+ * reference's CPU implementation (file:line citations are relative to the reference tree,
+ * dreaming-panda/LightGBMv1).
+ *
+ * Conventions (same as the reference's C API, include/LightGBM/c_api.h:1300-1312, src/c_api.cpp:35-49):
+ *   - every function returns 0 on success, -1 on failure; lgbcu_last_error() returns a thread-local message;
+ *   - plain pointers and sizes only; all pointers are HOST pointers unless the name ends in _dev;
+ *   - there is no CPU fallback: if no CUDA device is usable every call fails with a message.
+ *
+ * Data model held in HBM by one LgbCuContext (= one TreeLearner + ScoreUpdater + Objective of the reference):
+ *   bins      u8  [num_data][row_stride]  row-major; element = the reference's single-feature-group encoding
+ *                                         (include/LightGBM/feature_group.h:32-50,153-165): 0 = most-frequent
+ *                                         bin, else bin + 1 - [most_freq_bin == 0]
+ *   grad,hess f32 [num_data]              (score_t, include/LightGBM/meta.h)
+ *   score     f64 [num_data]              (src/boosting/score_updater.hpp:21-125)
+ *   indices   i32 [2][num_data]           leaf-ordered row indices, ping-pong (src/treelearner/data_partition.hpp)
+ *   pool      i64 [num_leaves][total_bin][2]  per-leaf histograms, 64-bit fixed point, layout
+ *                                         identical to the reference's hist_t buffer (include/LightGBM/bin.h:32-42,
+ *                                         src/treelearner/feature_histogram.hpp:1150-1176)
+ */
+#ifndef LGBCU_H_
+#define LGBCU_H_
+
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#if defined(_WIN32)
+#define LGBCU_API __declspec(dllexport)
+#else
+#define LGBCU_API __attribute__((visibility("default")))
+#endif
+
+typedef struct LgbCuContext LgbCuContext;
+
+/* missing_type values: include/LightGBM/bin.h (enum MissingType { None, Zero, NaN }) */
+enum { LGBCU_MISSING_NONE = 0, LGBCU_MISSING_ZERO = 1, LGBCU_MISSING_NAN = 2 };
+/* objective kinds implemented on device (src/objective/*.hpp) */
+enum { LGBCU_OBJ_NONE = 0, LGBCU_OBJ_BINARY = 1, LGBCU_OBJ_L2 = 2, LGBCU_OBJ_LAMBDARANK = 3 };
+/* histogram kernel selection (LGBCU_HIST_AUTO picks by leaf size) */
+enum { LGBCU_HIST_AUTO = 0, LGBCU_HIST_GLOBAL_ATOMIC = 1, LGBCU_HIST_WARP_PRIVATE = 2 };
+
+/* Per inner feature meta: what FeatureMetainfo + BinMapper give the CPU path
+ * (src/treelearner/feature_histogram.hpp:25-38,1110-1148; include/LightGBM/bin.h:85-215). */
+typedef struct LgbCuFeatureMeta {
+  int32_t num_bin;        /* BinMapper::num_bin() */
+  int32_t most_freq_bin;  /* BinMapper::GetMostFreqBin() */
+  int32_t default_bin;    /* BinMapper::GetDefaultBin() */
+  int32_t missing_type;   /* LGBCU_MISSING_* */
+  int32_t real_index;     /* Dataset::RealFeatureIndex(inner) -- used for the tie-break of SplitInfo::operator> */
+  int32_t reserved;
+  double  penalty;        /* feature_contri (FeatureMetainfo::penalty) */
+} LgbCuFeatureMeta;
+
+/* Tree-growing parameters read by the path (include/LightGBM/config.h; used in
+ * src/treelearner/serial_tree_learner.cpp:274-297 and feature_histogram.hpp:853-1049). */
+typedef struct LgbCuTreeParams {
+  int32_t num_leaves;
+  int32_t max_depth;              /* <=0: no limit */
+  int32_t min_data_in_leaf;
+  int32_t reserved;
+  double  min_sum_hessian_in_leaf;
+  double  lambda_l1;
+  double  lambda_l2;
+  double  min_gain_to_split;
+  double  max_delta_step;         /* <=0: off */
+  double  path_smooth;            /* <=kEpsilon: off */
+} LgbCuTreeParams;
+
+/* POD twin of SplitInfo (src/treelearner/split_info.hpp:22-53), numerical splits only. */
+typedef struct LgbCuSplitInfo {
+  int32_t feature;        /* inner feature index, -1 if none */
+  int32_t real_feature;   /* real feature index, -1 if none */
+  int32_t threshold;      /* threshold in bin */
+  int32_t default_left;
+  int32_t left_count;
+  int32_t right_count;
+  double  gain;           /* kMinScore (-inf) if no split */
+  double  left_output, right_output;
+  double  left_sum_gradient, left_sum_hessian;
+  double  right_sum_gradient, right_sum_hessian;
+} LgbCuSplitInfo;
+
+/* One applied split, in application order; the host replays them through Tree::Split
+ * (src/io/tree.cpp:54-68, include/LightGBM/tree.h:459-501). */
+typedef struct LgbCuSplitRecord {
+  int32_t leaf;           /* leaf that was split (left child keeps this id) */
+  int32_t right_leaf;     /* id of the new right child */
+  int32_t feature;        /* inner feature */
+  int32_t real_feature;
+  int32_t threshold;      /* bin */
+  int32_t default_left;
+  int32_t left_count, right_count;      /* actual partition sizes (SplitInner update_cnt, serial_tree_learner.cpp:567-571) */
+  float   gain;                          /* (float)(gain + min_gain_to_split), serial_tree_learner.cpp:583 */
+  int32_t reserved;
+  double  left_output, right_output;
+  double  left_sum_hessian, right_sum_hessian;
+  double  left_sum_gradient, right_sum_gradient;
+} LgbCuSplitRecord;
+
+LGBCU_API const char* lgbcu_last_error(void);
+/* number of CUDA devices visible (0 if none / no driver) */
+LGBCU_API int lgbcu_device_count(int* out);
+/* number of kernels launched by this library in this process (bench.py's gpu_launches) */
+LGBCU_API int64_t lgbcu_launch_count(void);
+
+LGBCU_API int lgbcu_create(int device_id, LgbCuContext** out);
+LGBCU_API int lgbcu_destroy(LgbCuContext* ctx);
+LGBCU_API int lgbcu_synchronize(LgbCuContext* ctx);
+
+/* A2: make the binned matrix resident.  `bins` is row-major [num_data][num_features] (host); it is copied
+ * into a row-major device matrix whose row stride is num_features rounded up to a multiple of 16 bytes.
+ * Replaces FeatureGroup/DenseBin storage (src/io/dense_bin.hpp:55-81) + TreeLearner::Init's view of it
+ * (src/treelearner/serial_tree_learner.cpp:28-69). */
+LGBCU_API int lgbcu_set_dataset(LgbCuContext* ctx, int32_t num_data, int32_t num_features,
+                                const uint8_t* bins, const LgbCuFeatureMeta* meta);
+/* Same, but the caller hands over column vectors (one u8[num_data] per inner feature), the layout the
+ * reference's DenseBin uses; the transpose to row-major happens on device. */
+LGBCU_API int lgbcu_set_dataset_columns(LgbCuContext* ctx, int32_t num_data, int32_t num_features,
+                                        const uint8_t* const* columns, const LgbCuFeatureMeta* meta);
+LGBCU_API int lgbcu_set_tree_params(LgbCuContext* ctx, const LgbCuTreeParams* params);
+LGBCU_API int lgbcu_set_hist_mode(LgbCuContext* ctx, int mode);
+
+/* Metadata (include/LightGBM/dataset.h Metadata: label_t = float labels/weights, int32 query boundaries) */
+LGBCU_API int lgbcu_set_label(LgbCuContext* ctx, const float* label, int32_t n);
+LGBCU_API int lgbcu_set_weight(LgbCuContext* ctx, const float* weight, int32_t n); /* weight==NULL clears */
+LGBCU_API int lgbcu_set_query(LgbCuContext* ctx, const int32_t* boundaries, int32_t num_queries);
+
+/* A9: objective on device.
+ * binary (src/objective/binary_objective.hpp:102-133): p0 = sigmoid, p1 = label_weight[neg], p2 = label_weight[pos]
+ * l2     (src/objective/regression_objective.hpp:125-140): no params
+ * lambdarank (src/objective/rank_objective.hpp:48-65,139-229): p0 = sigmoid, p1 = truncation_level, p2 = norm(0/1);
+ *        label_gain via lgbcu_set_label_gain */
+LGBCU_API int lgbcu_set_objective(LgbCuContext* ctx, int kind, double p0, double p1, double p2);
+LGBCU_API int lgbcu_set_label_gain(LgbCuContext* ctx, const double* label_gain, int32_t n);
+LGBCU_API int lgbcu_get_gradients(LgbCuContext* ctx);                      /* score -> grad,hess (device) */
+LGBCU_API int lgbcu_set_gradients(LgbCuContext* ctx, const float* grad, const float* hess, int32_t n);
+LGBCU_API int lgbcu_copy_gradients(LgbCuContext* ctx, float* grad, float* hess, int32_t n);
+
+/* A10: score (src/boosting/score_updater.hpp) */
+LGBCU_API int lgbcu_set_score(LgbCuContext* ctx, const double* score, int32_t n);      /* NULL -> zeros */
+LGBCU_API int lgbcu_add_score_const(LgbCuContext* ctx, double val);                    /* AddScore(double), :54-61 */
+LGBCU_API int lgbcu_copy_score(LgbCuContext* ctx, double* score, int32_t n);
+/* score[idx] += leaf_value[leaf(idx)] over the current partition
+ * (SerialTreeLearner::AddPredictionToScore, src/treelearner/serial_tree_learner.h:96-111) */
+LGBCU_API int lgbcu_add_score_by_partition(LgbCuContext* ctx, const double* leaf_value, int32_t num_leaves);
+
+/* A8: BeforeTrain (src/treelearner/serial_tree_learner.cpp:244-272): reset partition / leaf table / pool,
+ * root sums.  bag_indices==NULL -> all rows; feature_used==NULL -> all features (ColSampler by-tree mask). */
+LGBCU_API int lgbcu_begin_tree(LgbCuContext* ctx, const int32_t* bag_indices, int32_t bag_count,
+                               const int8_t* feature_used);
+
+/* A3+A4+A5: ConstructHistograms for `leaf` into its pool slot (Dataset::ConstructHistograms,
+ * src/io/dataset.cpp:1282-1383; DenseBin::ConstructHistogramInner, src/io/dense_bin.hpp:97-140). */
+LGBCU_API int lgbcu_hist_build(LgbCuContext* ctx, int32_t leaf);
+/* FixHistogram (src/io/dataset.cpp:1410-1428) applied; output = hist_t[2*total_bin] in the reference layout */
+LGBCU_API int lgbcu_hist_read(LgbCuContext* ctx, int32_t leaf, double* out, int64_t out_len);
+LGBCU_API int lgbcu_num_total_bin(LgbCuContext* ctx, int32_t* out);
+/* A5: larger = parent - smaller in the parent's slot (FeatureHistogram::Subtract, feature_histogram.hpp:79-83) */
+LGBCU_API int lgbcu_hist_subtract(LgbCuContext* ctx, int32_t parent_leaf_slot_owner, int32_t smaller_leaf);
+
+/* A6: FindBestThreshold over all used features of `leaf` + per-leaf argmax
+ * (feature_histogram.hpp:85-95,853-1049; serial_tree_learner.cpp:358-425,701-736). */
+LGBCU_API int lgbcu_find_best_split(LgbCuContext* ctx, int32_t leaf, LgbCuSplitInfo* out);
+
+/* A7: DataPartition::Split (src/treelearner/data_partition.hpp:101-120 -> dense_bin.hpp:173-307). */
+LGBCU_API int lgbcu_partition(LgbCuContext* ctx, int32_t leaf, int32_t inner_feature, int32_t threshold,
+                              int32_t default_left, int32_t right_leaf, int32_t* left_count);
+LGBCU_API int lgbcu_leaf_indices(LgbCuContext* ctx, int32_t leaf, int32_t* out, int32_t capacity, int32_t* count);
+/* set LeafSplits sums of a leaf by hand (step-wise tests; SplitInner does it in train_tree) */
+LGBCU_API int lgbcu_set_leaf_sums(LgbCuContext* ctx, int32_t leaf, double sum_g, double sum_h, double output);
+LGBCU_API int lgbcu_get_leaf_sums(LgbCuContext* ctx, int32_t leaf, double* sum_g, double* sum_h, int32_t* count);
+
+/* A8: the whole SerialTreeLearner::Train loop (serial_tree_learner.cpp:152-202) with device-side control:
+ * no host round trip per split.  Call lgbcu_begin_tree first.  records has room for num_leaves-1 entries. */
+LGBCU_API int lgbcu_train_tree(LgbCuContext* ctx, LgbCuSplitRecord* records, int32_t* num_splits);
+
+/* A11: data-parallel (src/treelearner/data_parallel_tree_learner.cpp) -- communicator plumbing.
+ * unique_id is NCCL's 128-byte id; rank 0 creates it, the caller broadcasts it (torch.distributed / MPI / file). */
+LGBCU_API int lgbcu_comm_unique_id(uint8_t* id128);
+LGBCU_API int lgbcu_comm_init(LgbCuContext* ctx, const uint8_t* id128, int32_t rank, int32_t world_size);
+LGBCU_API int lgbcu_comm_destroy(LgbCuContext* ctx);
+
+/* instrumentation for bench.py: device-time (ms, CUDA events on the context's stream) spent in the histogram
+ * kernel since the last reset, its launch count and the algorithmic bytes it processed
+ * (n*(G+8) [+4n if indexed] + total_bin*16 per call). */
+LGBCU_API int lgbcu_profile_enable(LgbCuContext* ctx, int on);
+LGBCU_API int lgbcu_profile_read(LgbCuContext* ctx, double* hist_ms, int64_t* hist_calls, double* hist_bytes,
+                                 int reset);
+
+#ifdef __cplusplus
+}
+#endif
+#endif  /* LGBCU_H_ */

@@ -1,0 +1,101 @@
+// Device-side state of the B200 tree learner.  Everything a tree needs while it grows lives in HBM; the
+// host only enqueues a fixed kernel sequence per split and reads the split records back once per tree.
+#pragma once
+#include <cuda_runtime.h>
+#include <stdint.h>
+#include "lgbcu.h"
+
+// reference constants (include/LightGBM/meta.h:52-56): float literals widened to double
+#define LGB_EPS        ((double)1e-15f)
+#define LGB_ZERO_THR   ((double)1e-35f)
+#define LGB_MIN_SCORE  (-__longlong_as_double(0x7ff0000000000000LL))  /* -inf */
+
+typedef long long i64;
+
+// One histogram entry: (sum_gradient, sum_hessian) in 64-bit fixed point.  Position in a leaf's buffer is
+// identical to the reference's hist_t pair (include/LightGBM/bin.h:32-42).
+struct __align__(16) HistEntry { i64 g; i64 h; };
+
+struct DevFeat {
+  int num_bin;       // BinMapper::num_bin
+  int offset;        // FeatureMetainfo::offset = [most_freq_bin == 0]
+  int mfb;           // most_freq_bin
+  int default_bin;
+  int missing_type;  // LGBCU_MISSING_*
+  int hist_base;     // first slot of the feature's (single-feature) group = group_bin_boundaries_[g]
+  int nslots;        // FeatureGroup::num_total_bin_ = 1 + num_bin - offset
+  int real_index;
+  double penalty;
+};
+
+struct DevSplit {    // SplitInfo, POD
+  double gain;
+  int feature;       // inner
+  int real_feature;
+  int threshold;
+  int default_left;
+  int left_count;
+  int right_count;
+  double left_output, right_output;
+  double left_sum_g, left_sum_h, right_sum_g, right_sum_h;
+};
+
+struct DevLeaf {     // DataPartition range + LeafSplits + pool slot of one leaf
+  int begin, count;  // range in indices[buf]
+  int slot;          // histogram pool slot
+  int depth;
+  int buf;           // which ping-pong index buffer holds this leaf's rows
+  int gcount;        // rows of this leaf over ALL ranks (== count on one GPU); what the split search calls num_data
+  double sum_g, sum_h;  // LeafSplits::sum_gradients/sum_hessians (from the parent's SplitInfo)
+  double output;        // LeafSplits::weight (leaf output before shrinkage)
+  i64 tot_g, tot_h;     // exact fixed-point totals of the rows histogrammed into this leaf's slot
+};
+
+struct DevCtl {
+  int num_leaves;    // leaves so far in the tree being grown
+  int done;          // 1 once no leaf has positive gain / num_leaves reached
+  int smaller, larger;  // LeafSplits pair of serial_tree_learner (larger = -1 for the root)
+  int skip_find;     // BeforeFindBestSplit returned false
+  int split_leaf, split_feature, split_threshold, split_default_left, split_right_leaf;
+  int split_left_count;
+  int num_splits;
+  unsigned max_g_bits, max_h_bits;  // max |g|, |h| as float bits
+  int root_identity; // root rows are 0..N-1 in order (no bagging): skip the index gather
+  int num_data;      // rows in the root
+  int kg, kh;        // fixed-point exponents
+  double scale_g, scale_h, inv_g, inv_h;
+  unsigned feat_done;  // "last block done" counter of k_find_split
+  unsigned pad0;
+  long long global_root;  // root rows over all ranks   } adjacent: one 2 x int64 sum all-reduce
+  long long global_rows;  // dataset rows over all ranks }
+  unsigned long long prof_hist_rows, prof_hist_rows_indexed, prof_hist_calls;
+};
+
+struct DevParams {   // LgbCuTreeParams + derived switches
+  int num_leaves, max_depth, min_data_in_leaf;
+  int use_l1, use_max_output, use_smoothing;
+  double min_sum_hessian, lambda_l1, lambda_l2, min_gain_to_split, max_delta_step, path_smooth;
+};
+
+// Everything the kernels need, passed by value (fits in the 4 KB parameter space with room to spare).
+struct DevView {
+  int num_data, num_features, row_stride, total_bin, num_tiles16;
+  int data_parallel;         // 1: histograms are all-reduced across ranks, leaf counts are the global estimates
+  const uint8_t* bins;
+  const DevFeat* feats;
+  const int8_t* feat_used;   // ColSampler by-tree mask
+  int8_t* splittable;        // [num_leaves slots][num_features]  FeatureHistogram::is_splittable_
+  float* grad; float* hess;
+  int* indices[2];
+  HistEntry* pool;           // [num_leaves][total_bin]
+  DevLeaf* leaves;
+  DevSplit* best;            // best_split_per_leaf_
+  DevSplit* feat_best;       // [2][num_features] per-feature candidates of (smaller, larger)
+  DevCtl* ctl;
+  LgbCuSplitRecord* records;
+  int* tile_left;            // partition scratch: lefts per 1024-row tile, then exclusive offsets
+  unsigned* part_bits;       // partition scratch: 1 bit per row (1 = goes left)
+  DevParams p;
+};
+
+__device__ __forceinline__ int round_int(double x) { return (int)(x + 0.5f); }  // Common::RoundInt

@@ -1,0 +1,755 @@
+// extern "C" layer of the B200 tree learner: owns the device buffers and enqueues the kernels.
+// See include/lgbcu.h for the contract of each entry point and the reference code it stands in for.
+#include <algorithm>
+#include <atomic>
+#include <cstddef>
+#include <cstdarg>
+#include <cstdio>
+#include <cstring>
+#include <string>
+#include <vector>
+
+#include <dlfcn.h>
+#include <nccl.h>
+
+#include "lgbcu.h"
+#include "dev_types.cuh"
+#include "hist_kernels.cuh"
+#include "split_kernels.cuh"
+#include "partition_kernels.cuh"
+#include "misc_kernels.cuh"
+
+namespace {
+
+thread_local char g_err[1024] = "everything is fine";
+std::atomic<long long> g_launches{0};
+
+int fail(const char* fmt, ...) {
+  va_list ap;
+  va_start(ap, fmt);
+  vsnprintf(g_err, sizeof(g_err), fmt, ap);
+  va_end(ap);
+  return -1;
+}
+
+#define CU(call)                                                                                   \
+  do {                                                                                             \
+    cudaError_t e__ = (call);                                                                      \
+    if (e__ != cudaSuccess) return fail("CUDA error %s at %s:%d (%s)", cudaGetErrorString(e__), __FILE__, __LINE__, #call); \
+  } while (0)
+
+#define LAUNCH(kernel, grid, block, smem, stream, ...)                                             \
+  do {                                                                                             \
+    kernel<<<(grid), (block), (smem), (stream)>>>(__VA_ARGS__);                                    \
+    g_launches.fetch_add(1, std::memory_order_relaxed);                                            \
+  } while (0)
+
+#define NEED(cond, ...)                                                                            \
+  do {                                                                                             \
+    if (!(cond)) return fail(__VA_ARGS__);                                                         \
+  } while (0)
+
+#include "comm.cuh"
+
+template <typename T>
+cudaError_t dev_alloc(T** p, size_t n) {
+  if (*p) { cudaFree(*p); *p = nullptr; }
+  if (n == 0) n = 1;
+  return cudaMalloc(reinterpret_cast<void**>(p), n * sizeof(T));
+}
+
+}  // namespace
+
+struct RankParams {
+  double sigmoid = 1.0; int truncation_level = 20; int norm = 1;
+};
+
+struct LgbCuContext {
+  int device = 0;
+  // data-parallel
+  ncclComm_t comm = nullptr; int rank = 0, world = 1;
+  int num_sms = 148;
+  cudaStream_t stream = nullptr;
+  // dataset
+  int N = 0, F = 0, stride = 0, total_bin = 0, ntiles16 = 0;
+  uint8_t* d_bins = nullptr;
+  DevFeat* d_feats = nullptr;
+  std::vector<DevFeat> h_feats;
+  int8_t* d_feat_used = nullptr;
+  // per-row state
+  float *d_grad = nullptr, *d_hess = nullptr, *d_label = nullptr, *d_weight = nullptr;
+  bool has_weight = false, has_label = false;
+  double* d_score = nullptr;
+  int* d_indices[2] = {nullptr, nullptr};
+  unsigned* d_part_bits = nullptr;
+  int* d_tile_left = nullptr;
+  // query structure (lambdarank)
+  int* d_query = nullptr; int num_queries = 0; int max_query = 0;
+  std::vector<int> h_query;
+  double* d_label_gain = nullptr; int num_label_gain = 0;
+  double* d_inv_max_dcg = nullptr; float* d_sigmoid_table = nullptr;
+  RankParams rank_params;
+  bool rank_ready = false;
+  // tree state
+  DevParams params{}; bool params_set = false;
+  int alloc_leaves = 0;
+  HistEntry* d_pool = nullptr;
+  int8_t* d_splittable = nullptr;
+  DevLeaf* d_leaves = nullptr;
+  DevSplit *d_best = nullptr, *d_feat_best = nullptr;
+  DevCtl* d_ctl = nullptr;
+  LgbCuSplitRecord* d_records = nullptr;
+  double* d_leaf_value = nullptr;
+  double* d_export = nullptr;
+  // host staging (pinned)
+  LgbCuSplitRecord* h_records = nullptr;
+  DevCtl* h_ctl = nullptr;
+  DevLeaf* h_leaf = nullptr;
+  DevSplit* h_split = nullptr;
+  // config
+  int hist_mode = LGBCU_HIST_AUTO;
+  int objective = LGBCU_OBJ_NONE; double obj_p[3] = {0, 0, 0};
+  int root_count = 0; bool tree_begun = false;
+  // profiling
+  bool profile = false;
+  std::vector<cudaEvent_t> ev;
+  double prof_hist_ms = 0; long long prof_hist_calls = 0; double prof_hist_bytes = 0;
+
+  DevView view() const {
+    DevView V;
+    V.num_data = N; V.num_features = F; V.row_stride = stride; V.total_bin = total_bin; V.num_tiles16 = ntiles16;
+    V.bins = d_bins; V.feats = d_feats; V.feat_used = d_feat_used; V.splittable = d_splittable;
+    V.grad = d_grad; V.hess = d_hess; V.indices[0] = d_indices[0]; V.indices[1] = d_indices[1];
+    V.pool = d_pool; V.leaves = d_leaves; V.best = d_best; V.feat_best = d_feat_best; V.ctl = d_ctl;
+    V.records = d_records; V.tile_left = d_tile_left; V.part_bits = d_part_bits; V.p = params;
+    V.data_parallel = comm != nullptr ? 1 : 0;
+    return V;
+  }
+};
+
+namespace {
+
+int grid_for(const LgbCuContext* c, long long work, int block, int per_sm = 8) {
+  long long g = (work + block - 1) / block;
+  const long long cap = (long long)c->num_sms * per_sm;
+  if (g > cap) g = cap;
+  if (g < 1) g = 1;
+  return (int)g;
+}
+
+int ensure_tree_buffers(LgbCuContext* c) {
+  NEED(c->F > 0 && c->N > 0, "lgbcu: dataset not set");
+  NEED(c->params_set, "lgbcu: tree params not set");
+  const int L = c->params.num_leaves;
+  if (c->alloc_leaves == L && c->d_pool) return 0;
+  CU(cudaSetDevice(c->device));
+  CU(dev_alloc(&c->d_pool, (size_t)L * c->total_bin));
+  CU(dev_alloc(&c->d_splittable, (size_t)L * c->F));
+  CU(dev_alloc(&c->d_leaves, (size_t)L));
+  CU(dev_alloc(&c->d_best, (size_t)L));
+  CU(dev_alloc(&c->d_records, (size_t)L));
+  CU(dev_alloc(&c->d_leaf_value, (size_t)L));
+  if (c->h_records) cudaFreeHost(c->h_records);
+  CU(cudaMallocHost(reinterpret_cast<void**>(&c->h_records), sizeof(LgbCuSplitRecord) * (size_t)L));
+  CU(cudaMemsetAsync(c->d_splittable, 0, (size_t)L * c->F, c->stream));
+  c->alloc_leaves = L;
+  return 0;
+}
+
+int launch_hist(LgbCuContext* c, int leaf_arg) {
+  const DevView V = c->view();
+  const int mode = c->hist_mode;
+  if (mode == LGBCU_HIST_GLOBAL_ATOMIC || mode == LGBCU_HIST_AUTO) {
+    const int regime = mode == LGBCU_HIST_AUTO ? 1 : 0;
+    // small leaves: enough threads for HIST_SMALL_LEAF_ROWS rows; forced mode: whole-GPU grid
+    const long long work = regime == 1 ? (long long)HIST_SMALL_LEAF_ROWS * c->ntiles16 : (long long)c->N * c->ntiles16;
+    LAUNCH(k_hist_global, grid_for(c, work, 256), 256, 0, c->stream, V, leaf_arg, regime);
+  }
+  if (mode == LGBCU_HIST_WARP_PRIVATE || mode == LGBCU_HIST_AUTO) {
+    const int regime = mode == LGBCU_HIST_AUTO ? 2 : 0;
+    LAUNCH(k_hist_warp_private, c->num_sms, HIST_WARPS_PER_BLOCK * 32, HIST_SMEM_BYTES, c->stream, V, leaf_arg, regime);
+  }
+  CU(cudaGetLastError());
+  return 0;
+}
+
+// max|g|, max|h| must be the same on every rank: the fixed-point scale is part of the wire format.
+int comm_allreduce_tree_setup(LgbCuContext* c) {
+  if (!c->comm) return 0;
+  char* base = reinterpret_cast<char*>(c->d_ctl);
+  void* mx = base + offsetof(DevCtl, max_g_bits);
+  void* rows = base + offsetof(DevCtl, global_root);
+  NC(g_nccl.AllReduce(mx, mx, 2, ncclUint32, ncclMax, c->comm, c->stream));
+  NC(g_nccl.AllReduce(rows, rows, 2, ncclInt64, ncclSum, c->comm, c->stream));
+  return 0;
+}
+
+// Split s builds the smaller leaf's histogram in pool slot s (slot 0 = root, then the fresh slot of split s
+// is s): known on the host without reading device state, so the collective can be enqueued blind.
+int comm_reduce_hist(LgbCuContext* c, int split_index) {
+  if (!c->comm) return 0;
+  HistEntry* slot = c->d_pool + (size_t)split_index * c->total_bin;
+  NC(g_nccl.AllReduce(slot, slot, (size_t)c->total_bin * 2, ncclInt64, ncclSum, c->comm, c->stream));
+  return 0;
+}
+
+int rank_prepare(LgbCuContext* c);
+int rank_launch(LgbCuContext* c);
+
+}  // namespace
+
+#include "rank_kernels.cuh"
+
+extern "C" {
+
+const char* lgbcu_last_error(void) { return g_err; }
+
+int lgbcu_device_count(int* out) {
+  int n = 0;
+  cudaError_t e = cudaGetDeviceCount(&n);
+  if (e != cudaSuccess) { *out = 0; cudaGetLastError(); return 0; }
+  *out = n;
+  return 0;
+}
+
+int64_t lgbcu_launch_count(void) { return g_launches.load(); }
+
+int lgbcu_create(int device_id, LgbCuContext** out) {
+  NEED(out != nullptr, "lgbcu_create: out is NULL");
+  int n = 0;
+  cudaError_t e = cudaGetDeviceCount(&n);
+  if (e != cudaSuccess || n == 0) {
+    cudaGetLastError();
+    return fail("lgbcu_create: no CUDA device available (%s); this library has no CPU fallback",
+                e != cudaSuccess ? cudaGetErrorString(e) : "device count is 0");
+  }
+  NEED(device_id >= 0 && device_id < n, "lgbcu_create: device %d out of range (have %d)", device_id, n);
+  CU(cudaSetDevice(device_id));
+  LgbCuContext* c = new LgbCuContext();
+  c->device = device_id;
+  cudaDeviceProp prop;
+  CU(cudaGetDeviceProperties(&prop, device_id));
+  c->num_sms = prop.multiProcessorCount;
+  CU(cudaStreamCreateWithFlags(&c->stream, cudaStreamNonBlocking));
+  CU(dev_alloc(&c->d_ctl, 1));
+  CU(cudaMemset(c->d_ctl, 0, sizeof(DevCtl)));
+  CU(cudaMallocHost(reinterpret_cast<void**>(&c->h_ctl), sizeof(DevCtl)));
+  CU(cudaMallocHost(reinterpret_cast<void**>(&c->h_leaf), sizeof(DevLeaf)));
+  CU(cudaMallocHost(reinterpret_cast<void**>(&c->h_split), sizeof(DevSplit)));
+  CU(cudaFuncSetAttribute(k_hist_warp_private, cudaFuncAttributeMaxDynamicSharedMemorySize, HIST_SMEM_BYTES));
+  *out = c;
+  return 0;
+}
+
+int lgbcu_destroy(LgbCuContext* c) {
+  if (!c) return 0;
+  cudaSetDevice(c->device);
+  cudaStreamSynchronize(c->stream);
+  lgbcu_comm_destroy(c);
+  void* ptrs[] = {c->d_bins, c->d_feats, c->d_feat_used, c->d_grad, c->d_hess, c->d_label, c->d_weight, c->d_score,
+                  c->d_indices[0], c->d_indices[1], c->d_part_bits, c->d_tile_left, c->d_query, c->d_label_gain,
+                  c->d_inv_max_dcg, c->d_sigmoid_table, c->d_pool, c->d_splittable, c->d_leaves, c->d_best,
+                  c->d_feat_best, c->d_ctl, c->d_records, c->d_leaf_value, c->d_export};
+  for (void* p : ptrs) if (p) cudaFree(p);
+  if (c->h_records) cudaFreeHost(c->h_records);
+  if (c->h_ctl) cudaFreeHost(c->h_ctl);
+  if (c->h_leaf) cudaFreeHost(c->h_leaf);
+  if (c->h_split) cudaFreeHost(c->h_split);
+  for (auto e : c->ev) cudaEventDestroy(e);
+  cudaStreamDestroy(c->stream);
+  delete c;
+  return 0;
+}
+
+int lgbcu_synchronize(LgbCuContext* c) {
+  NEED(c, "lgbcu: NULL context");
+  CU(cudaStreamSynchronize(c->stream));
+  return 0;
+}
+
+static int setup_dataset_common(LgbCuContext* c, int32_t num_data, int32_t num_features, const LgbCuFeatureMeta* meta) {
+  NEED(c, "lgbcu: NULL context");
+  NEED(num_data > 0 && num_features > 0 && meta, "lgbcu_set_dataset: empty dataset");
+  CU(cudaSetDevice(c->device));
+  c->N = num_data; c->F = num_features;
+  c->stride = (num_features + 15) & ~15;
+  c->ntiles16 = c->stride / 16;
+  c->h_feats.resize(num_features);
+  int base = 0;
+  for (int f = 0; f < num_features; ++f) {
+    DevFeat& d = c->h_feats[f];
+    const LgbCuFeatureMeta& m = meta[f];
+    NEED(m.num_bin >= 1 && m.most_freq_bin >= 0 && m.most_freq_bin < m.num_bin, "lgbcu_set_dataset: bad meta for feature %d", f);
+    d.num_bin = m.num_bin; d.mfb = m.most_freq_bin; d.offset = m.most_freq_bin == 0 ? 1 : 0;
+    d.default_bin = m.default_bin; d.missing_type = m.missing_type;
+    d.hist_base = base; d.nslots = 1 + d.num_bin - d.offset;
+    NEED(d.nslots <= 256, "lgbcu_set_dataset: feature %d needs %d stored values; only 8-bit bins are supported "
+         "(max_bin <= 255)", f, d.nslots);
+    d.real_index = m.real_index; d.penalty = m.penalty;
+    base += d.nslots;
+  }
+  c->total_bin = base;
+  CU(dev_alloc(&c->d_feats, (size_t)num_features));
+  CU(cudaMemcpyAsync(c->d_feats, c->h_feats.data(), sizeof(DevFeat) * num_features, cudaMemcpyHostToDevice, c->stream));
+  CU(dev_alloc(&c->d_bins, (size_t)num_data * c->stride));
+  CU(dev_alloc(&c->d_feat_used, (size_t)num_features));
+  CU(cudaMemsetAsync(c->d_feat_used, 1, num_features, c->stream));
+  CU(dev_alloc(&c->d_feat_best, (size_t)2 * num_features));
+  CU(dev_alloc(&c->d_grad, (size_t)num_data));
+  CU(dev_alloc(&c->d_hess, (size_t)num_data));
+  CU(dev_alloc(&c->d_score, (size_t)num_data));
+  CU(cudaMemsetAsync(c->d_score, 0, sizeof(double) * num_data, c->stream));
+  CU(dev_alloc(&c->d_indices[0], (size_t)num_data));
+  CU(dev_alloc(&c->d_indices[1], (size_t)num_data));
+  const size_t ntiles = ((size_t)num_data + PART_TILE - 1) / PART_TILE;
+  CU(dev_alloc(&c->d_tile_left, ntiles + 1));
+  CU(dev_alloc(&c->d_part_bits, ntiles * (PART_TILE / 32)));
+  CU(dev_alloc(&c->d_export, (size_t)2 * c->total_bin));
+  c->alloc_leaves = 0;  // pool depends on total_bin
+  c->has_label = c->has_weight = false;
+  c->tree_begun = false;
+  return 0;
+}
+
+int lgbcu_set_dataset(LgbCuContext* c, int32_t num_data, int32_t num_features, const uint8_t* bins,
+                      const LgbCuFeatureMeta* meta) {
+  NEED(bins, "lgbcu_set_dataset: bins is NULL");
+  if (setup_dataset_common(c, num_data, num_features, meta)) return -1;
+  CU(cudaMemsetAsync(c->d_bins, 0, (size_t)num_data * c->stride, c->stream));
+  CU(cudaMemcpy2DAsync(c->d_bins, c->stride, bins, num_features, num_features, num_data, cudaMemcpyHostToDevice, c->stream));
+  CU(cudaStreamSynchronize(c->stream));
+  return 0;
+}
+
+int lgbcu_set_dataset_columns(LgbCuContext* c, int32_t num_data, int32_t num_features, const uint8_t* const* columns,
+                              const LgbCuFeatureMeta* meta) {
+  NEED(columns, "lgbcu_set_dataset_columns: columns is NULL");
+  if (setup_dataset_common(c, num_data, num_features, meta)) return -1;
+  CU(cudaMemsetAsync(c->d_bins, 0, (size_t)num_data * c->stride, c->stream));
+  uint8_t* tmp[2] = {nullptr, nullptr};
+  CU(dev_alloc(&tmp[0], (size_t)num_data));
+  CU(dev_alloc(&tmp[1], (size_t)num_data));
+  for (int f = 0; f < num_features; ++f) {
+    uint8_t* t = tmp[f & 1];
+    if (f >= 2) CU(cudaStreamSynchronize(c->stream));  // the staging buffer two columns back is free again
+    CU(cudaMemcpyAsync(t, columns[f], num_data, cudaMemcpyHostToDevice, c->stream));
+    LAUNCH(k_scatter_column, grid_for(c, num_data, 256), 256, 0, c->stream, num_data, t, c->d_bins, c->stride, f);
+  }
+  CU(cudaGetLastError());
+  CU(cudaStreamSynchronize(c->stream));
+  cudaFree(tmp[0]); cudaFree(tmp[1]);
+  return 0;
+}
+
+int lgbcu_set_tree_params(LgbCuContext* c, const LgbCuTreeParams* p) {
+  NEED(c && p, "lgbcu_set_tree_params: NULL argument");
+  NEED(p->num_leaves >= 2, "lgbcu_set_tree_params: num_leaves must be >= 2");
+  DevParams d;
+  d.num_leaves = p->num_leaves; d.max_depth = p->max_depth; d.min_data_in_leaf = p->min_data_in_leaf;
+  d.min_sum_hessian = p->min_sum_hessian_in_leaf; d.lambda_l1 = p->lambda_l1; d.lambda_l2 = p->lambda_l2;
+  d.min_gain_to_split = p->min_gain_to_split; d.max_delta_step = p->max_delta_step; d.path_smooth = p->path_smooth;
+  d.use_l1 = p->lambda_l1 > 0; d.use_max_output = p->max_delta_step > 0; d.use_smoothing = p->path_smooth > LGB_EPS;
+  c->params = d; c->params_set = true;
+  return 0;
+}
+
+int lgbcu_set_hist_mode(LgbCuContext* c, int mode) {
+  NEED(c, "lgbcu: NULL context");
+  NEED(mode >= 0 && mode <= 2, "lgbcu_set_hist_mode: unknown mode %d", mode);
+  c->hist_mode = mode;
+  return 0;
+}
+
+int lgbcu_set_label(LgbCuContext* c, const float* label, int32_t n) {
+  NEED(c && label, "lgbcu_set_label: NULL argument");
+  NEED(n == c->N, "lgbcu_set_label: length %d != num_data %d", n, c->N);
+  CU(cudaSetDevice(c->device));
+  CU(dev_alloc(&c->d_label, (size_t)n));
+  CU(cudaMemcpyAsync(c->d_label, label, sizeof(float) * n, cudaMemcpyHostToDevice, c->stream));
+  CU(cudaStreamSynchronize(c->stream));
+  c->has_label = true; c->rank_ready = false;
+  return 0;
+}
+
+int lgbcu_set_weight(LgbCuContext* c, const float* weight, int32_t n) {
+  NEED(c, "lgbcu: NULL context");
+  if (!weight) { c->has_weight = false; return 0; }
+  NEED(n == c->N, "lgbcu_set_weight: length %d != num_data %d", n, c->N);
+  CU(cudaSetDevice(c->device));
+  CU(dev_alloc(&c->d_weight, (size_t)n));
+  CU(cudaMemcpyAsync(c->d_weight, weight, sizeof(float) * n, cudaMemcpyHostToDevice, c->stream));
+  CU(cudaStreamSynchronize(c->stream));
+  c->has_weight = true;
+  return 0;
+}
+
+int lgbcu_set_query(LgbCuContext* c, const int32_t* boundaries, int32_t num_queries) {
+  NEED(c && boundaries && num_queries > 0, "lgbcu_set_query: bad argument");
+  NEED(boundaries[0] == 0 && boundaries[num_queries] == c->N, "lgbcu_set_query: boundaries must span [0, num_data]");
+  CU(cudaSetDevice(c->device));
+  c->h_query.assign(boundaries, boundaries + num_queries + 1);
+  c->num_queries = num_queries;
+  c->max_query = 0;
+  for (int q = 0; q < num_queries; ++q) {
+    NEED(boundaries[q + 1] >= boundaries[q], "lgbcu_set_query: boundaries not monotone");
+    c->max_query = std::max(c->max_query, boundaries[q + 1] - boundaries[q]);
+  }
+  CU(dev_alloc(&c->d_query, (size_t)num_queries + 1));
+  CU(cudaMemcpyAsync(c->d_query, boundaries, sizeof(int) * (num_queries + 1), cudaMemcpyHostToDevice, c->stream));
+  CU(cudaStreamSynchronize(c->stream));
+  c->rank_ready = false;
+  return 0;
+}
+
+int lgbcu_set_objective(LgbCuContext* c, int kind, double p0, double p1, double p2) {
+  NEED(c, "lgbcu: NULL context");
+  NEED(kind >= LGBCU_OBJ_NONE && kind <= LGBCU_OBJ_LAMBDARANK, "lgbcu_set_objective: unknown kind %d", kind);
+  if (kind == LGBCU_OBJ_BINARY || kind == LGBCU_OBJ_LAMBDARANK) NEED(p0 > 0, "Sigmoid parameter %f should be greater than zero", p0);
+  c->objective = kind; c->obj_p[0] = p0; c->obj_p[1] = p1; c->obj_p[2] = p2;
+  c->rank_ready = false;
+  return 0;
+}
+
+int lgbcu_set_label_gain(LgbCuContext* c, const double* label_gain, int32_t n) {
+  NEED(c && label_gain && n > 0, "lgbcu_set_label_gain: bad argument");
+  CU(cudaSetDevice(c->device));
+  CU(dev_alloc(&c->d_label_gain, (size_t)n));
+  CU(cudaMemcpyAsync(c->d_label_gain, label_gain, sizeof(double) * n, cudaMemcpyHostToDevice, c->stream));
+  CU(cudaStreamSynchronize(c->stream));
+  c->num_label_gain = n; c->rank_ready = false;
+  return 0;
+}
+
+int lgbcu_get_gradients(LgbCuContext* c) {
+  NEED(c && c->N > 0, "lgbcu_get_gradients: dataset not set");
+  NEED(c->has_label, "lgbcu_get_gradients: label not set");
+  CU(cudaSetDevice(c->device));
+  const float* w = c->has_weight ? c->d_weight : nullptr;
+  const int g = grid_for(c, c->N, 256);
+  if (c->objective == LGBCU_OBJ_BINARY) {
+    LAUNCH(k_grad_binary, g, 256, 0, c->stream, c->N, c->d_score, c->d_label, w, c->obj_p[0], c->obj_p[1], c->obj_p[2], c->d_grad, c->d_hess);
+  } else if (c->objective == LGBCU_OBJ_L2) {
+    LAUNCH(k_grad_l2, g, 256, 0, c->stream, c->N, c->d_score, c->d_label, w, c->d_grad, c->d_hess);
+  } else if (c->objective == LGBCU_OBJ_LAMBDARANK) {
+    if (rank_prepare(c)) return -1;
+    if (rank_launch(c)) return -1;
+  } else {
+    return fail("lgbcu_get_gradients: no objective set");
+  }
+  CU(cudaGetLastError());
+  return 0;
+}
+
+int lgbcu_set_gradients(LgbCuContext* c, const float* grad, const float* hess, int32_t n) {
+  NEED(c && grad && hess, "lgbcu_set_gradients: NULL argument");
+  NEED(n == c->N, "lgbcu_set_gradients: length %d != num_data %d", n, c->N);
+  CU(cudaSetDevice(c->device));
+  CU(cudaMemcpyAsync(c->d_grad, grad, sizeof(float) * n, cudaMemcpyHostToDevice, c->stream));
+  CU(cudaMemcpyAsync(c->d_hess, hess, sizeof(float) * n, cudaMemcpyHostToDevice, c->stream));
+  CU(cudaStreamSynchronize(c->stream));
+  return 0;
+}
+
+int lgbcu_copy_gradients(LgbCuContext* c, float* grad, float* hess, int32_t n) {
+  NEED(c && grad && hess && n == c->N, "lgbcu_copy_gradients: bad argument");
+  CU(cudaSetDevice(c->device));
+  CU(cudaMemcpyAsync(grad, c->d_grad, sizeof(float) * n, cudaMemcpyDeviceToHost, c->stream));
+  CU(cudaMemcpyAsync(hess, c->d_hess, sizeof(float) * n, cudaMemcpyDeviceToHost, c->stream));
+  CU(cudaStreamSynchronize(c->stream));
+  return 0;
+}
+
+int lgbcu_set_score(LgbCuContext* c, const double* score, int32_t n) {
+  NEED(c && c->N > 0, "lgbcu_set_score: dataset not set");
+  CU(cudaSetDevice(c->device));
+  if (!score) { CU(cudaMemsetAsync(c->d_score, 0, sizeof(double) * c->N, c->stream)); return 0; }
+  NEED(n == c->N, "lgbcu_set_score: length %d != num_data %d", n, c->N);
+  CU(cudaMemcpyAsync(c->d_score, score, sizeof(double) * n, cudaMemcpyHostToDevice, c->stream));
+  CU(cudaStreamSynchronize(c->stream));
+  return 0;
+}
+
+int lgbcu_add_score_const(LgbCuContext* c, double val) {
+  NEED(c && c->N > 0, "lgbcu_add_score_const: dataset not set");
+  CU(cudaSetDevice(c->device));
+  LAUNCH(k_add_const, grid_for(c, c->N, 256), 256, 0, c->stream, c->N, c->d_score, val);
+  CU(cudaGetLastError());
+  return 0;
+}
+
+int lgbcu_copy_score(LgbCuContext* c, double* score, int32_t n) {
+  NEED(c && score && n == c->N, "lgbcu_copy_score: bad argument");
+  CU(cudaSetDevice(c->device));
+  CU(cudaMemcpyAsync(score, c->d_score, sizeof(double) * n, cudaMemcpyDeviceToHost, c->stream));
+  CU(cudaStreamSynchronize(c->stream));
+  return 0;
+}
+
+int lgbcu_add_score_by_partition(LgbCuContext* c, const double* leaf_value, int32_t num_leaves) {
+  NEED(c && leaf_value, "lgbcu_add_score_by_partition: NULL argument");
+  NEED(c->tree_begun, "lgbcu_add_score_by_partition: no tree has been grown");
+  NEED(num_leaves >= 1 && num_leaves <= c->alloc_leaves, "lgbcu_add_score_by_partition: num_leaves %d out of range", num_leaves);
+  CU(cudaSetDevice(c->device));
+  CU(cudaMemcpyAsync(c->d_leaf_value, leaf_value, sizeof(double) * num_leaves, cudaMemcpyHostToDevice, c->stream));
+  const DevView V = c->view();
+  int gx = grid_for(c, (c->root_count + num_leaves - 1) / num_leaves, 256, 4);
+  if (gx > 64) gx = 64;
+  LAUNCH(k_add_score_partition, dim3(gx, num_leaves), 256, 0, c->stream, V, c->d_leaf_value, c->d_score);
+  CU(cudaGetLastError());
+  // leaf_value is pageable host memory: the async copy above has been staged by the time it returns
+  return 0;
+}
+
+int lgbcu_begin_tree(LgbCuContext* c, const int32_t* bag_indices, int32_t bag_count, const int8_t* feature_used) {
+  NEED(c, "lgbcu: NULL context");
+  CU(cudaSetDevice(c->device));
+  if (ensure_tree_buffers(c)) return -1;
+  int identity = 1;
+  if (bag_indices) {
+    NEED(bag_count > 0 && bag_count <= c->N, "lgbcu_begin_tree: bag_count %d out of range", bag_count);
+    CU(cudaMemcpyAsync(c->d_indices[0], bag_indices, sizeof(int) * bag_count, cudaMemcpyHostToDevice, c->stream));
+    c->root_count = bag_count;
+    identity = 0;
+  } else {
+    LAUNCH(k_iota, grid_for(c, c->N, 256), 256, 0, c->stream, c->N, c->d_indices[0]);
+    c->root_count = c->N;
+  }
+  if (feature_used) {
+    CU(cudaMemcpyAsync(c->d_feat_used, feature_used, c->F, cudaMemcpyHostToDevice, c->stream));
+  } else {
+    CU(cudaMemsetAsync(c->d_feat_used, 1, c->F, c->stream));
+  }
+  CU(cudaMemsetAsync(c->d_pool, 0, sizeof(HistEntry) * (size_t)c->params.num_leaves * c->total_bin, c->stream));
+  LAUNCH(k_reset_ctl_max, 1, 1, 0, c->stream, c->d_ctl, c->root_count, c->N);
+  LAUNCH(k_absmax, grid_for(c, c->N, 256), 256, 0, c->stream, c->N, c->d_grad, c->d_hess, c->d_ctl);
+  if (comm_allreduce_tree_setup(c)) return -1;
+  LAUNCH(k_prepare_tree, 1, 256, 0, c->stream, c->view(), c->root_count, identity);
+  CU(cudaGetLastError());
+  if (bag_indices || feature_used) CU(cudaStreamSynchronize(c->stream));  // caller may reuse its buffers
+  c->tree_begun = true;
+  return 0;
+}
+
+int lgbcu_num_total_bin(LgbCuContext* c, int32_t* out) {
+  NEED(c && out, "lgbcu_num_total_bin: NULL argument");
+  *out = c->total_bin;
+  return 0;
+}
+
+int lgbcu_hist_build(LgbCuContext* c, int32_t leaf) {
+  NEED(c && c->tree_begun, "lgbcu_hist_build: call lgbcu_begin_tree first");
+  NEED(leaf >= 0 && leaf < c->params.num_leaves, "lgbcu_hist_build: leaf %d out of range", leaf);
+  CU(cudaSetDevice(c->device));
+  const DevView V = c->view();
+  LAUNCH(k_zero_slot, grid_for(c, c->total_bin, 256), 256, 0, c->stream, V, leaf);
+  cudaEvent_t e0 = nullptr, e1 = nullptr;
+  if (c->profile) {
+    if (c->ev.size() < 2) { c->ev.resize(2); CU(cudaEventCreate(&c->ev[0])); CU(cudaEventCreate(&c->ev[1])); }
+    e0 = c->ev[0]; e1 = c->ev[1];
+    CU(cudaEventRecord(e0, c->stream));
+  }
+  if (launch_hist(c, leaf)) return -1;
+  if (c->profile) {
+    CU(cudaEventRecord(e1, c->stream));
+    CU(cudaEventSynchronize(e1));
+    float ms = 0; CU(cudaEventElapsedTime(&ms, e0, e1));
+    c->prof_hist_ms += ms;
+  }
+  if (leaf == 0) LAUNCH(k_root_sums, 1, 32, 0, c->stream, V);
+  CU(cudaGetLastError());
+  return 0;
+}
+
+int lgbcu_hist_read(LgbCuContext* c, int32_t leaf, double* out, int64_t out_len) {
+  NEED(c && out && c->tree_begun, "lgbcu_hist_read: bad argument / no tree begun");
+  NEED(out_len == 2LL * c->total_bin, "lgbcu_hist_read: out_len %lld != 2*total_bin %d", (long long)out_len, 2 * c->total_bin);
+  NEED(leaf >= 0 && leaf < c->params.num_leaves, "lgbcu_hist_read: leaf %d out of range", leaf);
+  CU(cudaSetDevice(c->device));
+  LAUNCH(k_hist_export, c->F, 256, 0, c->stream, c->view(), leaf, c->d_export);
+  CU(cudaGetLastError());
+  CU(cudaMemcpyAsync(out, c->d_export, sizeof(double) * 2 * c->total_bin, cudaMemcpyDeviceToHost, c->stream));
+  CU(cudaStreamSynchronize(c->stream));
+  return 0;
+}
+
+int lgbcu_hist_subtract(LgbCuContext* c, int32_t parent_leaf, int32_t smaller_leaf) {
+  NEED(c && c->tree_begun, "lgbcu_hist_subtract: no tree begun");
+  CU(cudaSetDevice(c->device));
+  LAUNCH(k_hist_subtract, grid_for(c, c->total_bin, 256), 256, 0, c->stream, c->view(), parent_leaf, smaller_leaf);
+  CU(cudaGetLastError());
+  return 0;
+}
+
+int lgbcu_find_best_split(LgbCuContext* c, int32_t leaf, LgbCuSplitInfo* out) {
+  NEED(c && out && c->tree_begun, "lgbcu_find_best_split: bad argument / no tree begun");
+  NEED(leaf >= 0 && leaf < c->params.num_leaves, "lgbcu_find_best_split: leaf %d out of range", leaf);
+  CU(cudaSetDevice(c->device));
+  LAUNCH(k_find_split, c->F, 64, 0, c->stream, c->view(), 1, leaf);
+  CU(cudaGetLastError());
+  CU(cudaMemcpyAsync(c->h_split, c->d_best + leaf, sizeof(DevSplit), cudaMemcpyDeviceToHost, c->stream));
+  CU(cudaStreamSynchronize(c->stream));
+  const DevSplit& s = *c->h_split;
+  out->feature = s.feature; out->real_feature = s.real_feature; out->threshold = s.threshold;
+  out->default_left = s.default_left; out->left_count = s.left_count; out->right_count = s.right_count;
+  out->gain = s.gain; out->left_output = s.left_output; out->right_output = s.right_output;
+  out->left_sum_gradient = s.left_sum_g; out->left_sum_hessian = s.left_sum_h;
+  out->right_sum_gradient = s.right_sum_g; out->right_sum_hessian = s.right_sum_h;
+  return 0;
+}
+
+int lgbcu_partition(LgbCuContext* c, int32_t leaf, int32_t inner_feature, int32_t threshold, int32_t default_left,
+                    int32_t right_leaf, int32_t* left_count) {
+  NEED(c && left_count && c->tree_begun, "lgbcu_partition: bad argument / no tree begun");
+  NEED(leaf >= 0 && leaf < c->params.num_leaves && right_leaf > 0 && right_leaf < c->params.num_leaves && leaf != right_leaf,
+       "lgbcu_partition: leaf ids out of range");
+  NEED(inner_feature >= 0 && inner_feature < c->F, "lgbcu_partition: feature %d out of range", inner_feature);
+  CU(cudaSetDevice(c->device));
+  const DevView V = c->view();
+  LAUNCH(k_set_split, 1, 1, 0, c->stream, V, leaf, inner_feature, threshold, default_left, right_leaf);
+  LAUNCH(k_part_flags, grid_for(c, c->N, PART_TILE), PART_THREADS, 0, c->stream, V);
+  LAUNCH(k_part_scan, 1, 1024, 0, c->stream, V, 1);
+  LAUNCH(k_part_scatter, grid_for(c, c->N, PART_TILE), PART_THREADS, 0, c->stream, V, 0);
+  CU(cudaGetLastError());
+  CU(cudaMemcpyAsync(c->h_ctl, c->d_ctl, sizeof(DevCtl), cudaMemcpyDeviceToHost, c->stream));
+  CU(cudaStreamSynchronize(c->stream));
+  *left_count = c->h_ctl->split_left_count;
+  return 0;
+}
+
+int lgbcu_leaf_indices(LgbCuContext* c, int32_t leaf, int32_t* out, int32_t capacity, int32_t* count) {
+  NEED(c && count && c->tree_begun, "lgbcu_leaf_indices: bad argument / no tree begun");
+  NEED(leaf >= 0 && leaf < c->params.num_leaves, "lgbcu_leaf_indices: leaf %d out of range", leaf);
+  CU(cudaSetDevice(c->device));
+  CU(cudaMemcpyAsync(c->h_leaf, c->d_leaves + leaf, sizeof(DevLeaf), cudaMemcpyDeviceToHost, c->stream));
+  CU(cudaStreamSynchronize(c->stream));
+  const DevLeaf L = *c->h_leaf;
+  *count = L.count;
+  if (out) {
+    NEED(capacity >= L.count, "lgbcu_leaf_indices: capacity %d < leaf count %d", capacity, L.count);
+    if (L.count > 0) {
+      CU(cudaMemcpyAsync(out, c->d_indices[L.buf] + L.begin, sizeof(int) * L.count, cudaMemcpyDeviceToHost, c->stream));
+      CU(cudaStreamSynchronize(c->stream));
+    }
+  }
+  return 0;
+}
+
+int lgbcu_set_leaf_sums(LgbCuContext* c, int32_t leaf, double sum_g, double sum_h, double output) {
+  NEED(c && c->tree_begun, "lgbcu_set_leaf_sums: no tree begun");
+  NEED(leaf >= 0 && leaf < c->params.num_leaves, "lgbcu_set_leaf_sums: leaf %d out of range", leaf);
+  CU(cudaSetDevice(c->device));
+  LAUNCH(k_set_leaf_sums, 1, 1, 0, c->stream, c->view(), leaf, sum_g, sum_h, output);
+  CU(cudaGetLastError());
+  return 0;
+}
+
+int lgbcu_get_leaf_sums(LgbCuContext* c, int32_t leaf, double* sum_g, double* sum_h, int32_t* count) {
+  NEED(c && c->tree_begun, "lgbcu_get_leaf_sums: no tree begun");
+  NEED(leaf >= 0 && leaf < c->params.num_leaves, "lgbcu_get_leaf_sums: leaf %d out of range", leaf);
+  CU(cudaSetDevice(c->device));
+  CU(cudaMemcpyAsync(c->h_leaf, c->d_leaves + leaf, sizeof(DevLeaf), cudaMemcpyDeviceToHost, c->stream));
+  CU(cudaStreamSynchronize(c->stream));
+  if (sum_g) *sum_g = c->h_leaf->sum_g;
+  if (sum_h) *sum_h = c->h_leaf->sum_h;
+  if (count) *count = c->h_leaf->count;
+  return 0;
+}
+
+int lgbcu_train_tree(LgbCuContext* c, LgbCuSplitRecord* records, int32_t* num_splits) {
+  NEED(c && records && num_splits, "lgbcu_train_tree: NULL argument");
+  NEED(c->tree_begun, "lgbcu_train_tree: call lgbcu_begin_tree first");
+  CU(cudaSetDevice(c->device));
+  const DevView V = c->view();
+  const int L = c->params.num_leaves;
+  const int part_grid = grid_for(c, c->root_count, PART_TILE);
+  const bool prof = c->profile;
+  if (prof && (int)c->ev.size() < 2 * L) {
+    const size_t old = c->ev.size();
+    c->ev.resize(2 * L);
+    for (size_t i = old; i < c->ev.size(); ++i) CU(cudaEventCreate(&c->ev[i]));
+  }
+  for (int s = 0; s < L - 1; ++s) {
+    if (prof) CU(cudaEventRecord(c->ev[2 * s], c->stream));
+    if (launch_hist(c, -1)) return -1;
+    if (prof) CU(cudaEventRecord(c->ev[2 * s + 1], c->stream));
+    if (comm_reduce_hist(c, s)) return -1;
+    if (s == 0) LAUNCH(k_root_sums, 1, 32, 0, c->stream, V);
+    LAUNCH(k_find_split, c->F, 64, 0, c->stream, V, 0, -1);
+    LAUNCH(k_part_flags, part_grid, PART_THREADS, 0, c->stream, V);
+    LAUNCH(k_part_scan, 1, 1024, 0, c->stream, V, 0);
+    LAUNCH(k_part_scatter, part_grid, PART_THREADS, 0, c->stream, V, 0);
+  }
+  CU(cudaGetLastError());
+  CU(cudaMemcpyAsync(c->h_ctl, c->d_ctl, sizeof(DevCtl), cudaMemcpyDeviceToHost, c->stream));
+  CU(cudaMemcpyAsync(c->h_records, c->d_records, sizeof(LgbCuSplitRecord) * (size_t)(L - 1), cudaMemcpyDeviceToHost, c->stream));
+  CU(cudaStreamSynchronize(c->stream));
+  const int n = c->h_ctl->num_splits;
+  NEED(n >= 0 && n <= L - 1, "lgbcu_train_tree: corrupt split count %d", n);
+  std::memcpy(records, c->h_records, sizeof(LgbCuSplitRecord) * (size_t)n);
+  *num_splits = n;
+  if (prof) {
+    for (int s = 0; s < L - 1; ++s) {
+      float ms = 0; CU(cudaEventElapsedTime(&ms, c->ev[2 * s], c->ev[2 * s + 1]));
+      c->prof_hist_ms += ms;
+    }
+  }
+  return 0;
+}
+
+int lgbcu_profile_enable(LgbCuContext* c, int on) {
+  NEED(c, "lgbcu: NULL context");
+  c->profile = on != 0;
+  return 0;
+}
+
+int lgbcu_profile_read(LgbCuContext* c, double* hist_ms, int64_t* hist_calls, double* hist_bytes, int reset) {
+  NEED(c, "lgbcu: NULL context");
+  CU(cudaSetDevice(c->device));
+  CU(cudaMemcpyAsync(c->h_ctl, c->d_ctl, sizeof(DevCtl), cudaMemcpyDeviceToHost, c->stream));
+  CU(cudaStreamSynchronize(c->stream));
+  const unsigned long long rows = c->h_ctl->prof_hist_rows, rows_idx = c->h_ctl->prof_hist_rows_indexed;
+  const unsigned long long calls = c->h_ctl->prof_hist_calls;
+  // B_hist(n) = n*(G + 4 + 4) [+ 4n if indexed] + total_bin*16
+  const double bytes = (double)rows * (c->F + 8) + (double)rows_idx * (c->F + 12) + (double)calls * c->total_bin * 16.0;
+  if (hist_ms) *hist_ms = c->prof_hist_ms;
+  if (hist_calls) *hist_calls = (int64_t)calls;
+  if (hist_bytes) *hist_bytes = bytes;
+  if (reset) {
+    c->prof_hist_ms = 0;
+    CU(cudaMemsetAsync(&c->d_ctl->prof_hist_rows, 0, 3 * sizeof(unsigned long long), c->stream));
+    CU(cudaStreamSynchronize(c->stream));
+  }
+  return 0;
+}
+
+int lgbcu_comm_unique_id(uint8_t* id128) {
+  NEED(id128, "lgbcu_comm_unique_id: NULL argument");
+  if (nccl_load()) return -1;
+  ncclUniqueId id;
+  NC(g_nccl.GetUniqueId(&id));
+  static_assert(sizeof(id) == 128, "ncclUniqueId is expected to be 128 bytes");
+  std::memcpy(id128, &id, 128);
+  return 0;
+}
+
+int lgbcu_comm_init(LgbCuContext* c, const uint8_t* id128, int32_t rank, int32_t world_size) {
+  NEED(c && id128, "lgbcu_comm_init: NULL argument");
+  NEED(world_size >= 1 && rank >= 0 && rank < world_size, "lgbcu_comm_init: bad rank %d / world %d", rank, world_size);
+  if (world_size == 1) { c->rank = 0; c->world = 1; return 0; }
+  if (nccl_load()) return -1;
+  CU(cudaSetDevice(c->device));
+  ncclUniqueId id;
+  std::memcpy(&id, id128, 128);
+  NC(g_nccl.CommInitRank(&c->comm, world_size, id, rank));
+  c->rank = rank; c->world = world_size;
+  return 0;
+}
+
+int lgbcu_comm_destroy(LgbCuContext* c) {
+  if (!c || !c->comm) return 0;
+  g_nccl.CommDestroy(c->comm);
+  c->comm = nullptr; c->world = 1; c->rank = 0;
+  return 0;
+}
+
+}  // extern "C"

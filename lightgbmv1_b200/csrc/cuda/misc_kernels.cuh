@@ -1,0 +1,180 @@
+// Objective gradients (A9), score update (A10), per-tree preparation (A8) and layout helpers.
+#pragma once
+#include "dev_types.cuh"
+
+// ---------------------------------------------------------------------------------------------------------
+// BinaryLogloss::GetGradients (src/objective/binary_objective.hpp:102-133)
+__global__ void k_grad_binary(int n, const double* __restrict__ score, const float* __restrict__ label,
+                              const float* __restrict__ weight, double sigmoid, double w_neg, double w_pos,
+                              float* __restrict__ grad, float* __restrict__ hess) {
+  for (int i = blockIdx.x * blockDim.x + threadIdx.x; i < n; i += gridDim.x * blockDim.x) {
+    const int is_pos = label[i] > 0;
+    const int lab = is_pos ? 1 : -1;
+    const double lw = is_pos ? w_pos : w_neg;
+    const double response = -lab * sigmoid / (1.0f + exp(lab * sigmoid * score[i]));
+    const double abs_response = fabs(response);
+    if (weight == nullptr) {
+      grad[i] = (float)(response * lw);
+      hess[i] = (float)(abs_response * (sigmoid - abs_response) * lw);
+    } else {
+      grad[i] = (float)(response * lw * weight[i]);
+      hess[i] = (float)(abs_response * (sigmoid - abs_response) * lw * weight[i]);
+    }
+  }
+}
+
+// RegressionL2loss::GetGradients (src/objective/regression_objective.hpp:125-140)
+__global__ void k_grad_l2(int n, const double* __restrict__ score, const float* __restrict__ label,
+                          const float* __restrict__ weight, float* __restrict__ grad, float* __restrict__ hess) {
+  for (int i = blockIdx.x * blockDim.x + threadIdx.x; i < n; i += gridDim.x * blockDim.x) {
+    if (weight == nullptr) {
+      grad[i] = (float)(score[i] - label[i]);
+      hess[i] = 1.0f;
+    } else {
+      grad[i] = (float)((score[i] - label[i]) * weight[i]);
+      hess[i] = (float)(weight[i]);
+    }
+  }
+}
+
+// max |g|, max |h| as float bit patterns (non-negative floats order like unsigned ints)
+__global__ void k_absmax(int n, const float* __restrict__ grad, const float* __restrict__ hess, DevCtl* ctl) {
+  unsigned mg = 0, mh = 0;
+  for (int i = blockIdx.x * blockDim.x + threadIdx.x; i < n; i += gridDim.x * blockDim.x) {
+    mg = max(mg, __float_as_uint(fabsf(grad[i])));
+    mh = max(mh, __float_as_uint(fabsf(hess[i])));
+  }
+  for (int o = 16; o > 0; o >>= 1) {
+    mg = max(mg, __shfl_xor_sync(0xffffffffu, mg, o));
+    mh = max(mh, __shfl_xor_sync(0xffffffffu, mh, o));
+  }
+  if ((threadIdx.x & 31) == 0) {
+    if (mg) atomicMax(&ctl->max_g_bits, mg);
+    if (mh) atomicMax(&ctl->max_h_bits, mh);
+  }
+}
+
+// 2^k such that  max|v| * 2^k * rows < 2^62 : sums of `rows` fixed-point values cannot overflow an int64.
+__device__ __forceinline__ int fixed_exponent(unsigned max_bits, long long rows) {
+  const float m = __uint_as_float(max_bits);
+  if (!(m > 0.f) || isinf(m) || isnan(m)) return 0;
+  int e; frexpf(m, &e);          // m < 2^e
+  int rb = 0; while ((1ll << rb) <= rows) ++rb;  // rows < 2^rb
+  int k = 62 - e - rb;
+  if (k > 900) k = 900;
+  if (k < -900) k = -900;
+  return k;
+}
+
+__global__ void k_reset_ctl_max(DevCtl* ctl, int root_count, int num_data) {
+  ctl->max_g_bits = 0; ctl->max_h_bits = 0;
+  ctl->global_root = root_count; ctl->global_rows = num_data;
+}
+
+// BeforeTrain (src/treelearner/serial_tree_learner.cpp:244-272) on device: reset the control block, the
+// root leaf and the per-leaf best splits; derive the fixed-point scales from max|g|, max|h|.
+// scale_rows = number of rows a histogram entry can sum over (global row count in data-parallel mode).
+__global__ void k_prepare_tree(DevView V, int root_count, int root_identity) {
+  DevCtl* c = V.ctl;
+  const long long scale_rows = c->global_rows;
+  const int groot = (int)c->global_root;
+  for (int l = threadIdx.x; l < V.p.num_leaves; l += blockDim.x) {
+    DevSplit none; none.gain = LGB_MIN_SCORE; none.feature = -1; none.real_feature = -1;
+    none.threshold = 0; none.default_left = 1; none.left_count = 0; none.right_count = 0;
+    none.left_output = none.right_output = 0; none.left_sum_g = none.left_sum_h = 0;
+    none.right_sum_g = none.right_sum_h = 0;
+    V.best[l] = none;
+    DevLeaf z; z.begin = 0; z.count = 0; z.slot = l; z.depth = 0; z.buf = 0; z.gcount = 0;
+    z.sum_g = z.sum_h = z.output = 0; z.tot_g = z.tot_h = 0;
+    if (l == 0) { z.count = root_count; z.gcount = groot; }
+    V.leaves[l] = z;
+  }
+  if (threadIdx.x == 0) {
+    c->num_leaves = 1; c->done = 0; c->smaller = 0; c->larger = -1;
+    c->split_leaf = c->split_feature = c->split_threshold = 0;
+    c->split_default_left = 0; c->split_right_leaf = 1; c->split_left_count = 0;
+    c->num_splits = 0; c->feat_done = 0;
+    c->root_identity = root_identity; c->num_data = root_count;
+    c->kg = fixed_exponent(c->max_g_bits, scale_rows);
+    c->kh = fixed_exponent(c->max_h_bits, scale_rows);
+    c->scale_g = ldexp(1.0, c->kg); c->inv_g = ldexp(1.0, -c->kg);
+    c->scale_h = ldexp(1.0, c->kh); c->inv_h = ldexp(1.0, -c->kh);
+    // BeforeFindBestSplit for the root: right child count is 0 (serial_tree_learner.h GetGlobalDataCountInLeaf)
+    c->skip_find = (0 < V.p.min_data_in_leaf * 2 && groot < V.p.min_data_in_leaf * 2) ? 1 : 0;
+    if (V.p.num_leaves < 2) c->done = 1;
+  }
+}
+
+__global__ void k_iota(int n, int* out) {
+  for (int i = blockIdx.x * blockDim.x + threadIdx.x; i < n; i += gridDim.x * blockDim.x) out[i] = i;
+}
+
+// step-wise API helpers ------------------------------------------------------------------------------------
+__global__ void k_set_split(DevView V, int leaf, int feature, int threshold, int default_left, int right_leaf) {
+  DevCtl* c = V.ctl;
+  c->split_leaf = leaf; c->split_feature = feature; c->split_threshold = threshold;
+  c->split_default_left = default_left; c->split_right_leaf = right_leaf; c->done = 0;
+}
+__global__ void k_set_leaf_sums(DevView V, int leaf, double sg, double sh, double out) {
+  V.leaves[leaf].sum_g = sg; V.leaves[leaf].sum_h = sh; V.leaves[leaf].output = out;
+}
+// step-wise lgbcu_hist_build: clear the leaf's pool slot and its exact totals before accumulating
+__global__ void k_zero_slot(DevView V, int leaf) {
+  HistEntry* a = V.pool + (size_t)V.leaves[leaf].slot * V.total_bin;
+  HistEntry z; z.g = 0; z.h = 0;
+  for (int i = blockIdx.x * blockDim.x + threadIdx.x; i < V.total_bin; i += gridDim.x * blockDim.x) a[i] = z;
+  if (blockIdx.x == 0 && threadIdx.x == 0) { V.leaves[leaf].tot_g = 0; V.leaves[leaf].tot_h = 0; }
+}
+
+// FixHistogram (src/io/dataset.cpp:1410-1428) for every feature of one slot, then conversion to hist_t doubles
+// in the reference layout.  One block per feature.
+__global__ void k_hist_export(DevView V, int leaf, double* out) {
+  const int slot = V.leaves[leaf].slot;
+  const int f = blockIdx.x;
+  const DevFeat F = V.feats[f];
+  const HistEntry* h = V.pool + (size_t)slot * V.total_bin + F.hist_base;
+  double* o = out + 2 * (size_t)F.hist_base;
+  const double ig = V.ctl->inv_g, ih = V.ctl->inv_h;
+  for (int s = threadIdx.x; s < F.nslots; s += blockDim.x) {
+    HistEntry e = h[s];
+    if (F.mfb > 0 && s == 1 + F.mfb) e = h[0];
+    o[2 * s] = (double)e.g * ig;
+    o[2 * s + 1] = (double)e.h * ih;
+  }
+}
+
+// larger = parent - smaller over a whole slot (FeatureHistogram::Subtract, feature_histogram.hpp:79-83)
+__global__ void k_hist_subtract(DevView V, int parent_leaf, int smaller_leaf) {
+  const int parent_slot = V.leaves[parent_leaf].slot, smaller_slot = V.leaves[smaller_leaf].slot;
+  HistEntry* a = V.pool + (size_t)parent_slot * V.total_bin;
+  const HistEntry* b = V.pool + (size_t)smaller_slot * V.total_bin;
+  for (int i = blockIdx.x * blockDim.x + threadIdx.x; i < V.total_bin; i += gridDim.x * blockDim.x) {
+    HistEntry e = a[i]; const HistEntry s = b[i];
+    e.g -= s.g; e.h -= s.h; a[i] = e;
+  }
+}
+
+// SerialTreeLearner::AddPredictionToScore (src/treelearner/serial_tree_learner.h:96-111):
+// score[idx] += leaf_value[leaf] for every row of every leaf range.  grid = (blocks, num_leaves)
+__global__ void k_add_score_partition(DevView V, const double* __restrict__ leaf_value, double* __restrict__ score) {
+  const int leaf = blockIdx.y;
+  const DevLeaf L = V.leaves[leaf];
+  const double v = leaf_value[leaf];
+  const int* idx = V.indices[L.buf] + L.begin;
+  for (int i = blockIdx.x * blockDim.x + threadIdx.x; i < L.count; i += gridDim.x * blockDim.x) {
+    score[idx[i]] += v;
+  }
+}
+
+// ScoreUpdater::AddScore(double) (src/boosting/score_updater.hpp:54-61)
+__global__ void k_add_const(int n, double* score, double v) {
+  for (int i = blockIdx.x * blockDim.x + threadIdx.x; i < n; i += gridDim.x * blockDim.x) score[i] += v;
+}
+
+// column vectors -> row-major matrix (one warp-wide 32-row strip per step; coalesced on the column side)
+__global__ void k_scatter_column(int n, const uint8_t* __restrict__ col, uint8_t* __restrict__ bins, int row_stride,
+                                 int f) {
+  for (int i = blockIdx.x * blockDim.x + threadIdx.x; i < n; i += gridDim.x * blockDim.x) {
+    bins[(size_t)i * row_stride + f] = col[i];
+  }
+}

@@ -1,0 +1,240 @@
+// Data partition (replaces DataPartition::Split, src/treelearner/data_partition.hpp:101-120;
+// ParallelPartitionRunner::Run, include/LightGBM/utils/threading.h:105-172; DenseBin::SplitInner,
+// src/io/dense_bin.hpp:173-253 for single-feature groups) and the host bookkeeping that follows it in
+// SerialTreeLearner::SplitInner (serial_tree_learner.cpp:541-659) and BeforeFindBestSplit (:274-314).
+//
+// Stable two-way compaction in three launches, all sized for the worst case and driven by DevCtl:
+//   k_part_flags   : per row, gather the split feature's stored bin, decide left/right, warp-ballot the
+//                    decisions into a bit mask and count lefts per 1024-row tile;
+//   k_part_scan    : one block; exclusive scan of the tile counts, then the control step (leaf table, split
+//                    record, smaller/larger choice, depth / min_data gates);
+//   k_part_scatter : per row, rank = tile offset + popc prefix of the ballot words; write the row index into
+//                    the other ping-pong buffer, lefts first -- order inside each side is preserved.
+#pragma once
+#include "dev_types.cuh"
+
+#define PART_THREADS 256
+#define PART_REPS 4
+#define PART_TILE (PART_THREADS * PART_REPS) /* 1024 rows = 32 ballot words */
+
+// DenseBin::SplitInner for a single-feature group (min_bin = 1, USE_MIN_BIN = false).
+struct SplitRule {
+  int th, t_zero, maxb;
+  int default_left_side;   // side of stored value 0 (the most-frequent bin) when it is not the missing bin
+  int missing_left;        // side of missing rows
+  int miss_zero, miss_na, mfb_zero, mfb_na;
+  int wide;                // min_bin < max_bin
+  int maxbin_left;         // narrow case: side of the single non-default slot
+};
+
+__device__ __forceinline__ SplitRule make_rule(const DevFeat& F, int threshold, int default_left) {
+  SplitRule r;
+  r.maxb = F.nslots - 1;
+  r.th = threshold + 1;
+  r.t_zero = 1 + F.default_bin;
+  if (F.mfb == 0) { --r.th; --r.t_zero; }
+  r.default_left_side = F.mfb <= threshold;
+  r.miss_zero = F.missing_type == LGBCU_MISSING_ZERO;
+  r.miss_na = F.missing_type == LGBCU_MISSING_NAN;
+  r.mfb_zero = r.miss_zero && F.default_bin == F.mfb;
+  r.mfb_na = r.miss_na && (r.maxb == F.mfb + 1) && F.mfb > 0;
+  r.missing_left = (r.miss_zero || r.miss_na) ? (default_left != 0) : 0;
+  r.wide = 1 < r.maxb;
+  r.maxbin_left = r.maxb <= r.th;
+  return r;
+}
+
+__device__ __forceinline__ bool goes_left(const SplitRule& r, int bin) {
+  if (r.wide) {
+    if ((r.miss_zero && !r.mfb_zero && bin == r.t_zero) || (r.miss_na && !r.mfb_na && bin == r.maxb)) {
+      return r.missing_left;
+    } else if (bin == 0) {
+      if ((r.miss_na && r.mfb_na) || (r.miss_zero && r.mfb_zero)) return r.missing_left;
+      return r.default_left_side;
+    }
+    return !(bin > r.th);
+  }
+  if (r.miss_zero && !r.mfb_zero && bin == r.t_zero) return r.missing_left;
+  if (bin != r.maxb) {
+    if ((r.miss_na && r.mfb_na) || (r.miss_zero && r.mfb_zero)) return r.missing_left;
+    return r.default_left_side;
+  }
+  if (r.miss_na && !r.mfb_na) return r.missing_left;
+  return r.maxbin_left;
+}
+
+__global__ void __launch_bounds__(PART_THREADS) k_part_flags(DevView V) {
+  const DevCtl* c = V.ctl;
+  if (c->done) return;
+  const DevLeaf L = V.leaves[c->split_leaf];
+  const DevFeat F = V.feats[c->split_feature];
+  const SplitRule rule = make_rule(F, c->split_threshold, c->split_default_left);
+  const int* src = V.indices[L.buf] + L.begin;
+  const uint8_t* col = V.bins + c->split_feature;
+  const int ntiles = (L.count + PART_TILE - 1) / PART_TILE;
+  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+  __shared__ int s_cnt[PART_THREADS / 32];
+  for (int tile = blockIdx.x; tile < ntiles; tile += gridDim.x) {
+    int lefts = 0;
+#pragma unroll
+    for (int r = 0; r < PART_REPS; ++r) {
+      const int pos = tile * PART_TILE + r * PART_THREADS + threadIdx.x;
+      bool left = false;
+      if (pos < L.count) {
+        const int row = src[pos];
+        left = goes_left(rule, col[(size_t)row * V.row_stride]);
+      }
+      const unsigned word = __ballot_sync(0xffffffffu, left);
+      if (lane == 0) {
+        V.part_bits[(size_t)tile * (PART_TILE / 32) + r * (PART_THREADS / 32) + warp] = word;
+        lefts += __popc(word);
+      }
+    }
+    if (lane == 0) s_cnt[warp] = lefts;
+    __syncthreads();
+    if (threadIdx.x == 0) {
+      int t = 0;
+      for (int w = 0; w < PART_THREADS / 32; ++w) t += s_cnt[w];
+      V.tile_left[tile] = t;
+    }
+    __syncthreads();
+  }
+}
+
+// mode 0: training (control step runs); mode 1: step-wise API (only counts/ranges are updated, sums untouched)
+__global__ void __launch_bounds__(1024) k_part_scan(DevView V, int mode) {
+  DevCtl* c = V.ctl;
+  if (c->done) return;
+  const int leaf = c->split_leaf;
+  const DevLeaf L = V.leaves[leaf];
+  const int ntiles = (L.count + PART_TILE - 1) / PART_TILE;
+  __shared__ int s_warp[32];
+  __shared__ int s_carry;
+  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+  if (threadIdx.x == 0) s_carry = 0;
+  __syncthreads();
+  for (int base = 0; base < ntiles; base += 1024) {
+    const int i = base + threadIdx.x;
+    const int v = i < ntiles ? V.tile_left[i] : 0;
+    int inc = v;
+    for (int o = 1; o < 32; o <<= 1) {
+      const int x = __shfl_up_sync(0xffffffffu, inc, o);
+      if (lane >= o) inc += x;
+    }
+    if (lane == 31) s_warp[warp] = inc;
+    __syncthreads();
+    if (warp == 0) {
+      int w = s_warp[lane];
+      int winc = w;
+      for (int o = 1; o < 32; o <<= 1) {
+        const int x = __shfl_up_sync(0xffffffffu, winc, o);
+        if (lane >= o) winc += x;
+      }
+      s_warp[lane] = winc - w;  // exclusive prefix of warp sums
+    }
+    __syncthreads();
+    const int excl = s_carry + s_warp[warp] + inc - v;
+    if (i < ntiles) V.tile_left[i] = excl;
+    __syncthreads();
+    if (threadIdx.x == 1023) s_carry = excl + v;
+    __syncthreads();
+  }
+  if (threadIdx.x != 0) return;
+  const int left_cnt = s_carry, right_cnt = L.count - s_carry;
+  c->split_left_count = left_cnt;
+  const int R = c->split_right_leaf;
+  DevLeaf A = L, B = L;  // A = left child (keeps the id), B = right child (new id R)
+  A.count = left_cnt; A.buf = L.buf ^ 1; A.depth = L.depth + 1; A.gcount = left_cnt;
+  B.begin = L.begin + left_cnt; B.count = right_cnt; B.buf = L.buf ^ 1; B.depth = L.depth + 1; B.gcount = right_cnt;
+  A.tot_g = A.tot_h = B.tot_g = B.tot_h = 0;
+  if (mode == 1) {
+    B.slot = R;
+    V.leaves[leaf] = A;
+    V.leaves[R] = B;
+    if (c->num_leaves < R + 1) c->num_leaves = R + 1;
+    return;
+  }
+  const DevSplit s = V.best[leaf];
+  // SplitInner: on one GPU (update_cnt = true) the counts come from the partition; in data-parallel mode
+  // (update_cnt = false, data_parallel_tree_learner.cpp:250-256) they stay the global, hessian-derived counts of
+  // the SplitInfo, which every rank computed identically.  Everything else always comes from the SplitInfo.
+  const int gl = V.data_parallel ? s.left_count : left_cnt;
+  const int gr = V.data_parallel ? s.right_count : right_cnt;
+  A.gcount = gl; B.gcount = gr;
+  LgbCuSplitRecord rec;
+  rec.leaf = leaf; rec.right_leaf = R; rec.feature = s.feature; rec.real_feature = s.real_feature;
+  rec.threshold = s.threshold; rec.default_left = s.default_left;
+  rec.left_count = gl; rec.right_count = gr;
+  rec.gain = (float)(s.gain + V.p.min_gain_to_split); rec.reserved = 0;
+  rec.left_output = s.left_output; rec.right_output = s.right_output;
+  rec.left_sum_hessian = s.left_sum_h; rec.right_sum_hessian = s.right_sum_h;
+  rec.left_sum_gradient = s.left_sum_g; rec.right_sum_gradient = s.right_sum_g;
+  V.records[c->num_splits] = rec;
+  c->num_splits += 1;
+  A.sum_g = s.left_sum_g; A.sum_h = s.left_sum_h; A.output = s.left_output;
+  B.sum_g = s.right_sum_g; B.sum_h = s.right_sum_h; B.output = s.right_output;
+  // smaller / larger (serial_tree_learner.cpp:629-649) and the histogram-pool hand-over (:298-312): the
+  // larger child inherits the parent's slot (subtraction happens in place), the smaller gets a fresh one.
+  int smaller, larger;
+  if (gl < gr) { smaller = leaf; larger = R; A.slot = R; B.slot = L.slot; }
+  else { smaller = R; larger = leaf; B.slot = R; A.slot = L.slot; }
+  V.leaves[leaf] = A;
+  V.leaves[R] = B;
+  c->smaller = smaller; c->larger = larger;
+  c->num_leaves = R + 1;
+  // BeforeFindBestSplit gates (serial_tree_learner.cpp:274-297)
+  int skip = 0;
+  if (V.p.max_depth > 0 && A.depth >= V.p.max_depth) skip = 1;
+  if (!skip && gr < V.p.min_data_in_leaf * 2 && gl < V.p.min_data_in_leaf * 2) skip = 1;
+  if (skip) {
+    V.best[leaf].gain = LGB_MIN_SCORE;
+    DevSplit none; none.gain = LGB_MIN_SCORE; none.feature = -1; none.real_feature = -1;
+    V.best[R] = none;
+  }
+  c->skip_find = skip;
+  if (c->num_leaves >= V.p.num_leaves) c->done = 2;  // tree is full; nothing more to enqueue
+}
+
+__global__ void __launch_bounds__(PART_THREADS) k_part_scatter(DevView V, int parent_buf_arg) {
+  const DevCtl* c = V.ctl;
+  // done == 2 is set by the k_part_scan that just ran for the LAST split: its scatter must still happen
+  if (c->done == 1) return;
+  const int leaf = c->split_leaf;
+  const DevLeaf A = V.leaves[leaf];  // already the left child: begin unchanged, buf flipped
+  const int left_total = c->split_left_count;
+  const int count = left_total + V.leaves[c->split_right_leaf].count;
+  const int* src = V.indices[A.buf ^ 1] + A.begin;
+  int* dst = V.indices[A.buf] + A.begin;
+  const int ntiles = (count + PART_TILE - 1) / PART_TILE;
+  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+  (void)parent_buf_arg;
+  for (int tile = blockIdx.x; tile < ntiles; tile += gridDim.x) {
+    // every warp redundantly scans the tile's 32 ballot words (no block sync needed)
+    const unsigned myword = V.part_bits[(size_t)tile * (PART_TILE / 32) + lane];
+    const int pc = __popc(myword);
+    int inc = pc;
+    for (int o = 1; o < 32; o <<= 1) {
+      const int x = __shfl_up_sync(0xffffffffu, inc, o);
+      if (lane >= o) inc += x;
+    }
+    const int excl = inc - pc;
+    const int tile_off = V.tile_left[tile];
+#pragma unroll
+    for (int r = 0; r < PART_REPS; ++r) {
+      const int w = r * (PART_THREADS / 32) + warp;
+      const unsigned word = __shfl_sync(0xffffffffu, myword, w);
+      const int wpre = __shfl_sync(0xffffffffu, excl, w);
+      const int pos = tile * PART_TILE + w * 32 + lane;
+      if (pos < count) {
+        const unsigned lt = (1u << lane) - 1u;
+        const int row = src[pos];
+        if ((word >> lane) & 1u) {
+          dst[tile_off + wpre + __popc(word & lt)] = row;
+        } else {
+          const int rights_before = (tile * PART_TILE - tile_off) + (w * 32 - wpre) + __popc(~word & lt);
+          dst[left_total + rights_before] = row;
+        }
+      }
+    }
+  }
+}
