@@ -41,7 +41,7 @@ typedef struct LgbCuContext LgbCuContext;
 
 /* missing_type values: include/LightGBM/bin.h (enum MissingType { None, Zero, NaN }) */
 enum { LGBCU_MISSING_NONE = 0, LGBCU_MISSING_ZERO = 1, LGBCU_MISSING_NAN = 2 };
-/* objective kinds implemented on device (src/objective/*.hpp) */
+/* objective kinds implemented on device (src/objective/) */
 enum { LGBCU_OBJ_NONE = 0, LGBCU_OBJ_BINARY = 1, LGBCU_OBJ_L2 = 2, LGBCU_OBJ_LAMBDARANK = 3 };
 /* histogram kernel selection (LGBCU_HIST_AUTO picks by leaf size) */
 enum { LGBCU_HIST_AUTO = 0, LGBCU_HIST_GLOBAL_ATOMIC = 1, LGBCU_HIST_WARP_PRIVATE = 2 };
@@ -151,6 +151,16 @@ LGBCU_API int lgbcu_copy_score(LgbCuContext* ctx, double* score, int32_t n);
  * (SerialTreeLearner::AddPredictionToScore, src/treelearner/serial_tree_learner.h:96-111) */
 LGBCU_API int lgbcu_add_score_by_partition(LgbCuContext* ctx, const double* leaf_value, int32_t num_leaves);
 
+/* Tree::AddPredictionToScore on the resident binned matrix (src/io/tree.cpp:109-199; decision:
+ * include/LightGBM/tree.h:285-300).  rows == NULL -> every row; otherwise the listed rows (out-of-bag rows in
+ * GBDT::UpdateScore, src/boosting/gbdt.cpp:465-468).  rows_tag != 0 lets the library keep the uploaded row list:
+ * a call with the same non-zero tag and count reuses it.  decision_type as in the model file
+ * (bit 1 = default_left, bits 2-3 = missing type). */
+LGBCU_API int lgbcu_add_score_by_tree(LgbCuContext* ctx, int32_t num_leaves, const int32_t* split_feature_inner,
+                                      const int32_t* threshold_bin, const int8_t* decision_type,
+                                      const int32_t* left_child, const int32_t* right_child, const double* leaf_value,
+                                      const int32_t* rows, int32_t num_rows, int64_t rows_tag);
+
 /* A8: BeforeTrain (src/treelearner/serial_tree_learner.cpp:244-272): reset partition / leaf table / pool,
  * root sums.  bag_indices==NULL -> all rows; feature_used==NULL -> all features (ColSampler by-tree mask). */
 LGBCU_API int lgbcu_begin_tree(LgbCuContext* ctx, const int32_t* bag_indices, int32_t bag_count,
@@ -186,6 +196,9 @@ LGBCU_API int lgbcu_train_tree(LgbCuContext* ctx, LgbCuSplitRecord* records, int
 LGBCU_API int lgbcu_comm_unique_id(uint8_t* id128);
 LGBCU_API int lgbcu_comm_init(LgbCuContext* ctx, const uint8_t* id128, int32_t rank, int32_t world_size);
 LGBCU_API int lgbcu_comm_destroy(LgbCuContext* ctx);
+/* small host-side syncs of the data-parallel path (Network::GlobalSyncUpBySum / ByMean, include/LightGBM/network.h:
+ * 160-260): in-place sum over ranks of n <= 64 doubles.  No-op on one rank. */
+LGBCU_API int lgbcu_comm_allreduce_sum_f64(LgbCuContext* ctx, double* inout, int32_t n);
 
 /* instrumentation for bench.py: device-time (ms, CUDA events on the context's stream) spent in the histogram
  * kernel since the last reset, its launch count and the algorithmic bytes it processed

@@ -1,0 +1,111 @@
+/*
+ * lgbm_b200.h -- the drop-in boundary: the subset of the reference's C API (include/LightGBM/c_api.h) that sits in
+ * front of the training hot path, exported by lib_lightgbm_b200.so with the SAME names, argument order, types
+ * and 0 / -1 + LGBM_GetLastError convention (c_api.h:1300-1312, src/c_api.cpp:35-49), so that a caller bound to
+ * lib_lightgbm.so (python-package/lightgbm/basic.py, R, SWIG, tests/c_api_test/test_.py) can load this library
+ * instead.  Each declaration cites the reference declaration it replaces.
+ *
+ * Behavioural contract: same parameter strings (aliases, defaults) for the keys the path reads; `device_type` is
+ * accepted with cpu|gpu|cuda and always selects the CUDA learner (there is no CPU path); `tree_learner` is
+ * serial|data.  Parameters that would change the trees but are outside the path (categorical features, monotone
+ * constraints, dart/goss/rf, multiclass, ...) fail with a message instead of silently training something else.
+ */
+#ifndef LGBM_B200_H_
+#define LGBM_B200_H_
+
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define LGBM_B200_API __attribute__((visibility("default")))
+
+typedef void* DatasetHandle; /* c_api.h:23 */
+typedef void* BoosterHandle; /* c_api.h:24 */
+
+#define C_API_DTYPE_FLOAT32 (0) /* c_api.h:27-30 */
+#define C_API_DTYPE_FLOAT64 (1)
+#define C_API_DTYPE_INT32 (2)
+#define C_API_DTYPE_INT64 (3)
+#define C_API_PREDICT_NORMAL (0)    /* c_api.h:32-35 */
+#define C_API_PREDICT_RAW_SCORE (1)
+
+/* c_api.h:47 */
+LGBM_B200_API const char* LGBM_GetLastError(void);
+
+/* c_api.h:229-236  (src/c_api.cpp:998-1015 -> :1018-1100) */
+LGBM_B200_API int LGBM_DatasetCreateFromMat(const void* data, int data_type, int32_t nrow, int32_t ncol, int is_row_major,
+                                            const char* parameters, const DatasetHandle reference, DatasetHandle* out);
+/* c_api.h:344-348  (src/c_api.cpp:1422-1439) field_name: label | weight | group/query | init_score */
+LGBM_B200_API int LGBM_DatasetSetField(DatasetHandle handle, const char* field_name, const void* field_data,
+                                       int num_element, int type);
+/* c_api.h:380-381 */
+LGBM_B200_API int LGBM_DatasetGetNumData(DatasetHandle handle, int* out);
+/* c_api.h:389-390 */
+LGBM_B200_API int LGBM_DatasetGetNumFeature(DatasetHandle handle, int* out);
+/* c_api.h:311 */
+LGBM_B200_API int LGBM_DatasetFree(DatasetHandle handle);
+
+/* c_api.h:410-412  (src/c_api.cpp:1501-1509) */
+LGBM_B200_API int LGBM_BoosterCreate(const DatasetHandle train_data, const char* parameters, BoosterHandle* out);
+/* c_api.h:441 */
+LGBM_B200_API int LGBM_BoosterFree(BoosterHandle handle);
+/* c_api.h:505-506  (src/c_api.cpp:1598-1607) */
+LGBM_B200_API int LGBM_BoosterUpdateOneIter(BoosterHandle handle, int* is_finished);
+/* c_api.h:530-533  (src/c_api.cpp:1609-1625) custom objective: host float gradients / hessians */
+LGBM_B200_API int LGBM_BoosterUpdateOneIterCustom(BoosterHandle handle, const float* grad, const float* hess, int* is_finished);
+/* c_api.h:548-549 */
+LGBM_B200_API int LGBM_BoosterGetCurrentIteration(BoosterHandle handle, int* out_iteration);
+/* c_api.h:557-558 */
+LGBM_B200_API int LGBM_BoosterNumModelPerIteration(BoosterHandle handle, int* out_tree_per_iteration);
+/* c_api.h:566-567 */
+LGBM_B200_API int LGBM_BoosterNumberOfTotalModel(BoosterHandle handle, int* out_models);
+/* c_api.h:496-497 */
+LGBM_B200_API int LGBM_BoosterGetNumClasses(BoosterHandle handle, int* out_len);
+/* c_api.h:649-651  data_idx 0 = training data */
+LGBM_B200_API int LGBM_BoosterGetNumPredict(BoosterHandle handle, int data_idx, int64_t* out_len);
+/* c_api.h:663-666  scores of the training data after the objective's output transform */
+LGBM_B200_API int LGBM_BoosterGetPredict(BoosterHandle handle, int data_idx, int64_t* out_len, double* out_result);
+/* c_api.h:1007-1018  predict_type: C_API_PREDICT_NORMAL | C_API_PREDICT_RAW_SCORE (host tree walk; not on the hot path) */
+LGBM_B200_API int LGBM_BoosterPredictForMat(BoosterHandle handle, const void* data, int data_type, int32_t nrow, int32_t ncol,
+                                            int is_row_major, int predict_type, int start_iteration, int num_iteration,
+                                            const char* parameter, int64_t* out_len, double* out_result);
+/* c_api.h:1172-1178 */
+LGBM_B200_API int LGBM_BoosterSaveModelToString(BoosterHandle handle, int start_iteration, int num_iteration,
+                                                int feature_importance_type, int64_t buffer_len, int64_t* out_len,
+                                                char* out_str);
+/* c_api.h:1155-1159 */
+LGBM_B200_API int LGBM_BoosterSaveModel(BoosterHandle handle, int start_iteration, int num_iteration,
+                                        int feature_importance_type, const char* filename);
+
+/* Data-parallel rendezvous inside one NVLink box.  Replaces LGBM_NetworkInit (c_api.h:1266-1269: machine list +
+ * TCP ports) for tree_learner=data: the ranks share a 128-byte NCCL id instead of a socket mesh.  Rank 0 calls
+ * LGBM_NetworkGetNCCLUniqueId and hands the bytes to the other ranks by any means (torch.distributed, MPI, a
+ * file); every rank then calls LGBM_NetworkInitNCCL before LGBM_BoosterCreate.  State is thread-local, like the
+ * reference's Network (src/network/network.cpp:17-27). */
+LGBM_B200_API int LGBM_NetworkGetNCCLUniqueId(uint8_t* out_id128);
+LGBM_B200_API int LGBM_NetworkInitNCCL(const uint8_t* id128, int rank, int num_machines);
+/* c_api.h:1275 */
+LGBM_B200_API int LGBM_NetworkFree(void);
+
+/* ours: how many kernels this library has launched in this process (bench.py's gpu_launches) */
+LGBM_B200_API int64_t LGBM_B200_LaunchCount(void);
+/* ours: histogram-kernel instrumentation of a booster (device ms, calls, algorithmic bytes); see lgbcu.h */
+LGBM_B200_API int LGBM_B200_BoosterProfile(BoosterHandle handle, int enable, int reset, double* hist_ms,
+                                           int64_t* hist_calls, double* hist_bytes);
+
+/* ours: introspection used by the parity tests (the reference exposes the same facts through
+ * LGBM_DatasetDumpText, src/io/dataset.cpp:994-1044).  out_bins: [num_data][num_inner_features] BIN values
+ * (BinIterator::Get, not the stored encoding), row-major; real_index: real column of every inner feature. */
+LGBM_B200_API int LGBM_B200_DatasetNumInnerFeatures(DatasetHandle handle, int* out);
+LGBM_B200_API int LGBM_B200_DatasetDumpBins(DatasetHandle handle, int32_t* out_bins, int32_t* real_index);
+/* ours: bin mapper of one inner feature: meta[0..4] = num_bin, most_freq_bin, default_bin, missing_type, real index;
+ * upper_bounds receives min(num_bin, cap) doubles */
+LGBM_B200_API int LGBM_B200_DatasetFeatureInfo(DatasetHandle handle, int inner_feature, int32_t* meta5,
+                                               double* upper_bounds, int cap);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* LGBM_B200_H_ */

@@ -69,10 +69,10 @@ LGBCU_SYMBOLS = [
     "lgbcu_synchronize", "lgbcu_set_dataset", "lgbcu_set_dataset_columns", "lgbcu_set_tree_params",
     "lgbcu_set_hist_mode", "lgbcu_set_label", "lgbcu_set_weight", "lgbcu_set_query", "lgbcu_set_objective",
     "lgbcu_set_label_gain", "lgbcu_get_gradients", "lgbcu_set_gradients", "lgbcu_copy_gradients",
-    "lgbcu_set_score", "lgbcu_add_score_const", "lgbcu_copy_score", "lgbcu_add_score_by_partition",
+    "lgbcu_set_score", "lgbcu_add_score_const", "lgbcu_copy_score", "lgbcu_add_score_by_partition", "lgbcu_add_score_by_tree",
     "lgbcu_begin_tree", "lgbcu_hist_build", "lgbcu_hist_read", "lgbcu_num_total_bin", "lgbcu_hist_subtract",
     "lgbcu_find_best_split", "lgbcu_partition", "lgbcu_leaf_indices", "lgbcu_set_leaf_sums",
-    "lgbcu_get_leaf_sums", "lgbcu_train_tree", "lgbcu_comm_unique_id", "lgbcu_comm_init", "lgbcu_comm_destroy",
+    "lgbcu_get_leaf_sums", "lgbcu_train_tree", "lgbcu_comm_unique_id", "lgbcu_comm_init", "lgbcu_comm_destroy", "lgbcu_comm_allreduce_sum_f64",
     "lgbcu_profile_enable", "lgbcu_profile_read",
 ]
 
@@ -229,6 +229,20 @@ class CudaLearner:
     def add_score_by_partition(self, leaf_values) -> None:
         a = np.ascontiguousarray(leaf_values, dtype=np.float64)
         check(lib.lgbcu_add_score_by_partition(self._h, _ptr(a, C.c_double), C.c_int32(len(a))))
+
+    def add_score_by_tree(self, split_feature_inner, threshold_bin, decision_type, left_child, right_child,
+                          leaf_value, rows=None, rows_tag=0) -> None:
+        lv = np.ascontiguousarray(leaf_value, dtype=np.float64)
+        sf = np.ascontiguousarray(split_feature_inner, dtype=np.int32)
+        tb = np.ascontiguousarray(threshold_bin, dtype=np.int32)
+        dt = np.ascontiguousarray(decision_type, dtype=np.int8)
+        lc = np.ascontiguousarray(left_child, dtype=np.int32)
+        rc = np.ascontiguousarray(right_child, dtype=np.int32)
+        r = None if rows is None else np.ascontiguousarray(rows, dtype=np.int32)
+        check(lib.lgbcu_add_score_by_tree(self._h, C.c_int32(len(lv)), _ptr(sf, C.c_int32), _ptr(tb, C.c_int32),
+                                          _ptr(dt, C.c_int8), _ptr(lc, C.c_int32), _ptr(rc, C.c_int32),
+                                          _ptr(lv, C.c_double), None if r is None else _ptr(r, C.c_int32),
+                                          C.c_int32(0 if r is None else len(r)), C.c_int64(rows_tag)))
 
     # ---- tree steps
     def begin_tree(self, bag_indices=None, feature_used=None) -> None:

@@ -101,6 +101,10 @@ struct LgbCuContext {
   LgbCuSplitRecord* d_records = nullptr;
   double* d_leaf_value = nullptr;
   double* d_export = nullptr;
+  // tree upload for add_score_by_tree
+  int* d_tree_i32 = nullptr; signed char* d_tree_i8 = nullptr; double* d_tree_f64 = nullptr; int tree_cap = 0;
+  int* d_rows = nullptr; int rows_cap = 0; long long rows_tag = 0; int rows_count = 0;
+  double* d_scratch = nullptr;
   // host staging (pinned)
   LgbCuSplitRecord* h_records = nullptr;
   DevCtl* h_ctl = nullptr;
@@ -249,7 +253,8 @@ int lgbcu_destroy(LgbCuContext* c) {
   void* ptrs[] = {c->d_bins, c->d_feats, c->d_feat_used, c->d_grad, c->d_hess, c->d_label, c->d_weight, c->d_score,
                   c->d_indices[0], c->d_indices[1], c->d_part_bits, c->d_tile_left, c->d_query, c->d_label_gain,
                   c->d_inv_max_dcg, c->d_sigmoid_table, c->d_pool, c->d_splittable, c->d_leaves, c->d_best,
-                  c->d_feat_best, c->d_ctl, c->d_records, c->d_leaf_value, c->d_export};
+                  c->d_feat_best, c->d_ctl, c->d_records, c->d_leaf_value, c->d_export, c->d_tree_i32, c->d_tree_i8,
+                  c->d_tree_f64, c->d_rows, c->d_scratch};
   for (void* p : ptrs) if (p) cudaFree(p);
   if (c->h_records) cudaFreeHost(c->h_records);
   if (c->h_ctl) cudaFreeHost(c->h_ctl);
@@ -500,6 +505,55 @@ int lgbcu_add_score_by_partition(LgbCuContext* c, const double* leaf_value, int3
   return 0;
 }
 
+int lgbcu_add_score_by_tree(LgbCuContext* c, int32_t num_leaves, const int32_t* split_feature_inner,
+                            const int32_t* threshold_bin, const int8_t* decision_type, const int32_t* left_child,
+                            const int32_t* right_child, const double* leaf_value, const int32_t* rows, int32_t num_rows,
+                            int64_t rows_tag) {
+  NEED(c && c->N > 0, "lgbcu_add_score_by_tree: dataset not set");
+  NEED(num_leaves >= 1 && leaf_value, "lgbcu_add_score_by_tree: bad tree");
+  CU(cudaSetDevice(c->device));
+  const int n = rows ? num_rows : c->N;
+  if (n <= 0) return 0;
+  if (num_leaves == 1) {  // constant tree: score += leaf_value[0] (tree.cpp:110-118)
+    if (leaf_value[0] == 0.0) return 0;
+    NEED(rows == nullptr, "lgbcu_add_score_by_tree: constant tree over a row subset is not supported");
+    return lgbcu_add_score_const(c, leaf_value[0]);
+  }
+  NEED(split_feature_inner && threshold_bin && decision_type && left_child && right_child, "lgbcu_add_score_by_tree: NULL tree array");
+  const int ni = num_leaves - 1;
+  if (c->tree_cap < num_leaves) {
+    CU(dev_alloc(&c->d_tree_i32, (size_t)4 * num_leaves));
+    CU(dev_alloc(&c->d_tree_i8, (size_t)num_leaves));
+    CU(dev_alloc(&c->d_tree_f64, (size_t)num_leaves));
+    c->tree_cap = num_leaves;
+  }
+  for (int i = 0; i < ni; ++i) NEED(split_feature_inner[i] >= 0 && split_feature_inner[i] < c->F, "lgbcu_add_score_by_tree: split feature out of range");
+  int* d_feat = c->d_tree_i32, *d_thr = d_feat + num_leaves, *d_lc = d_thr + num_leaves, *d_rc = d_lc + num_leaves;
+  CU(cudaMemcpyAsync(d_feat, split_feature_inner, sizeof(int) * ni, cudaMemcpyHostToDevice, c->stream));
+  CU(cudaMemcpyAsync(d_thr, threshold_bin, sizeof(int) * ni, cudaMemcpyHostToDevice, c->stream));
+  CU(cudaMemcpyAsync(d_lc, left_child, sizeof(int) * ni, cudaMemcpyHostToDevice, c->stream));
+  CU(cudaMemcpyAsync(d_rc, right_child, sizeof(int) * ni, cudaMemcpyHostToDevice, c->stream));
+  CU(cudaMemcpyAsync(c->d_tree_i8, decision_type, ni, cudaMemcpyHostToDevice, c->stream));
+  CU(cudaMemcpyAsync(c->d_tree_f64, leaf_value, sizeof(double) * num_leaves, cudaMemcpyHostToDevice, c->stream));
+  const int* d_rows = nullptr;
+  if (rows) {
+    const bool reuse = rows_tag != 0 && rows_tag == c->rows_tag && num_rows == c->rows_count;
+    if (!reuse) {
+      if (c->rows_cap < num_rows) { CU(dev_alloc(&c->d_rows, (size_t)num_rows)); c->rows_cap = num_rows; }
+      CU(cudaMemcpyAsync(c->d_rows, rows, sizeof(int) * num_rows, cudaMemcpyHostToDevice, c->stream));
+      c->rows_tag = rows_tag; c->rows_count = num_rows;
+    }
+    d_rows = c->d_rows;
+  }
+  TreeDev T;
+  T.split_feature = d_feat; T.threshold_bin = d_thr; T.decision_type = c->d_tree_i8; T.left_child = d_lc; T.right_child = d_rc;
+  T.leaf_value = c->d_tree_f64; T.num_leaves = num_leaves;
+  LAUNCH(k_add_score_tree, grid_for(c, n, 256), 256, 0, c->stream, c->view(), T, d_rows, n, c->d_score);
+  CU(cudaGetLastError());
+  CU(cudaStreamSynchronize(c->stream));  // the caller's host arrays may go away
+  return 0;
+}
+
 int lgbcu_begin_tree(LgbCuContext* c, const int32_t* bag_indices, int32_t bag_count, const int8_t* feature_used) {
   NEED(c, "lgbcu: NULL context");
   CU(cudaSetDevice(c->device));
@@ -742,6 +796,18 @@ int lgbcu_comm_init(LgbCuContext* c, const uint8_t* id128, int32_t rank, int32_t
   std::memcpy(&id, id128, 128);
   NC(g_nccl.CommInitRank(&c->comm, world_size, id, rank));
   c->rank = rank; c->world = world_size;
+  return 0;
+}
+
+int lgbcu_comm_allreduce_sum_f64(LgbCuContext* c, double* inout, int32_t n) {
+  NEED(c && inout && n > 0 && n <= 64, "lgbcu_comm_allreduce_sum_f64: bad argument");
+  if (!c->comm) return 0;
+  CU(cudaSetDevice(c->device));
+  if (!c->d_scratch) CU(dev_alloc(&c->d_scratch, (size_t)64));
+  CU(cudaMemcpyAsync(c->d_scratch, inout, sizeof(double) * n, cudaMemcpyHostToDevice, c->stream));
+  NC(g_nccl.AllReduce(c->d_scratch, c->d_scratch, (size_t)n, ncclDouble, ncclSum, c->comm, c->stream));
+  CU(cudaMemcpyAsync(inout, c->d_scratch, sizeof(double) * n, cudaMemcpyDeviceToHost, c->stream));
+  CU(cudaStreamSynchronize(c->stream));
   return 0;
 }
 

@@ -178,3 +178,53 @@ __global__ void k_scatter_column(int n, const uint8_t* __restrict__ col, uint8_t
     bins[(size_t)i * row_stride + f] = col[i];
   }
 }
+
+// Tree::AddPredictionToScore on binned data (src/io/tree.cpp:109-199 with NumericalDecisionInner,
+// include/LightGBM/tree.h:285-300): walk the tree for each listed row (out-of-bag rows, or all rows).
+struct TreeDev {
+  const int* split_feature; const int* threshold_bin; const signed char* decision_type;
+  const int* left_child; const int* right_child; const double* leaf_value;
+  int num_leaves;
+};
+#define TREE_SMEM_NODES 1024
+__global__ void __launch_bounds__(256) k_add_score_tree(DevView V, TreeDev T, const int* __restrict__ rows, int n,
+                                                        double* __restrict__ score) {
+  __shared__ int s_feat[TREE_SMEM_NODES], s_thr[TREE_SMEM_NODES], s_left[TREE_SMEM_NODES], s_right[TREE_SMEM_NODES];
+  __shared__ signed char s_dt[TREE_SMEM_NODES];
+  const int ni = T.num_leaves - 1;
+  const bool cached = ni <= TREE_SMEM_NODES;
+  if (cached) {
+    for (int i = threadIdx.x; i < ni; i += blockDim.x) {
+      s_feat[i] = T.split_feature[i]; s_thr[i] = T.threshold_bin[i]; s_left[i] = T.left_child[i];
+      s_right[i] = T.right_child[i]; s_dt[i] = T.decision_type[i];
+    }
+    __syncthreads();
+  }
+  const int* feat = cached ? s_feat : T.split_feature;
+  const int* thr = cached ? s_thr : T.threshold_bin;
+  const int* lc = cached ? s_left : T.left_child;
+  const int* rc = cached ? s_right : T.right_child;
+  const signed char* dt = cached ? s_dt : T.decision_type;
+  for (int i = blockIdx.x * blockDim.x + threadIdx.x; i < n; i += gridDim.x * blockDim.x) {
+    const int row = rows ? rows[i] : i;
+    const uint8_t* r = V.bins + (size_t)row * V.row_stride;
+    int node = 0;
+    while (node >= 0) {
+      const int f = feat[node];
+      const DevFeat F = V.feats[f];
+      const int stored = r[f];
+      // DenseBinIterator::Get: stored value -> bin
+      const int bin = stored == 0 ? F.mfb : stored - 1 + F.offset;
+      const int missing_type = (dt[node] >> 2) & 3;
+      bool left;
+      if ((missing_type == LGBCU_MISSING_ZERO && bin == F.default_bin) ||
+          (missing_type == LGBCU_MISSING_NAN && bin == F.num_bin - 1)) {
+        left = (dt[node] & 2) != 0;
+      } else {
+        left = bin <= thr[node];
+      }
+      node = left ? lc[node] : rc[node];
+    }
+    score[row] += T.leaf_value[~node];
+  }
+}

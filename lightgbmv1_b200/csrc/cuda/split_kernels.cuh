@@ -256,6 +256,16 @@ __device__ void scan_feature_warp(const i64 (&gi)[BINS_PER_LANE], const i64 (&hi
   *splittable_out = splittable;
 }
 
+// ComputeBestSplitForFeature (serial_tree_learner.cpp:709-718): the reference tests `leaf_index() == 0`, which holds
+// for the root and for every later leaf that still carries id 0 (a left child keeps its parent's id): such a leaf's
+// "parent output" is its own unsmoothed output; every other leaf uses the output its parent's split assigned.
+__device__ __forceinline__ double parent_output_of(const DevLeaf& L, int leaf, const DevParams& P) {
+  if (leaf != 0) return L.output;
+  DevParams P0 = P;
+  P0.use_smoothing = 0;
+  return leaf_output(L.sum_g, L.sum_h, P0, L.gcount, 0.0);
+}
+
 // SplitInfo::operator> : larger gain, ties -> smaller real feature index (-1 counts as INT_MAX)
 __device__ __forceinline__ bool split_better(double ga, int fa, double gb, int fb) {
   if (fa == -1) fa = 0x7fffffff;
@@ -302,14 +312,7 @@ __global__ void __launch_bounds__(64) k_find_split(DevView V, int mode, int leaf
           }
           gi[k] = e.g; hi[k] = e.h;
         }
-        // ComputeBestSplitForFeature (serial_tree_learner.cpp:709-718): the root's "parent output" is its own
-        // unsmoothed output; every other leaf carries the output its parent's split gave it.
-        double parent_output = Ls.output;
-        if (smaller == 0 && (mode == 1 || c->num_leaves == 1)) {
-          DevParams P0 = V.p;
-          P0.use_smoothing = 0;
-          parent_output = leaf_output(Ls.sum_g, Ls.sum_h, P0, Ls.gcount, 0.0);
-        }
+        const double parent_output = parent_output_of(Ls, smaller, V.p);
         scan_feature_warp(gi, hi, nt, F, Ls.sum_g, Ls.sum_h, Ls.gcount, parent_output, V.p, inv_g, inv_h, &o, &sp);
         o.feature = f; o.real_feature = F.real_index;
       }
@@ -342,7 +345,7 @@ __global__ void __launch_bounds__(64) k_find_split(DevView V, int mode, int leaf
           HistEntry e; e.g = a.g - b.g; e.h = a.h - b.h;
           hl[0] = e;
         }
-        scan_feature_warp(gi, hi, nt, F, Ll.sum_g, Ll.sum_h, Ll.gcount, Ll.output, V.p, inv_g, inv_h, &o, &sp);
+        scan_feature_warp(gi, hi, nt, F, Ll.sum_g, Ll.sum_h, Ll.gcount, parent_output_of(Ll, larger, V.p), V.p, inv_g, inv_h, &o, &sp);
         o.feature = f; o.real_feature = F.real_index;
       }
       if (lane == 0) {

@@ -1,0 +1,222 @@
+#include "bin_mapper.h"
+
+#include <algorithm>
+#include <iomanip>
+
+namespace lgb {
+namespace {
+
+const double kInf = std::numeric_limits<double>::infinity();
+
+// GreedyFindBin (src/io/bin.cpp:78-155): equal-count bins over distinct values; values whose count reaches the
+// mean bin size get a bin of their own.
+std::vector<double> GreedyBounds(const double* vals, const int* cnts, int n_distinct, int max_bin, size_t total_cnt,
+                                 int min_data_in_bin) {
+  std::vector<double> bounds;
+  if (max_bin <= 0) Log::Fatal("Check failed: (max_bin) > (0)");
+  if (n_distinct <= max_bin) {
+    int acc = 0;
+    for (int i = 0; i + 1 < n_distinct; ++i) {
+      acc += cnts[i];
+      if (acc >= min_data_in_bin) {
+        const double mid = NextUp((vals[i] + vals[i + 1]) / 2.0);
+        if (bounds.empty() || !EqualOrdered(bounds.back(), mid)) {
+          bounds.push_back(mid);
+          acc = 0;
+        }
+      }
+    }
+    bounds.push_back(kInf);
+    return bounds;
+  }
+  if (min_data_in_bin > 0) {
+    max_bin = std::min(max_bin, static_cast<int>(total_cnt / min_data_in_bin));
+    max_bin = std::max(max_bin, 1);
+  }
+  double mean_size = static_cast<double>(total_cnt) / max_bin;
+  int rest_bins = max_bin;
+  int rest_cnt = static_cast<int>(total_cnt);
+  std::vector<bool> is_big(n_distinct, false);
+  for (int i = 0; i < n_distinct; ++i) {
+    if (cnts[i] >= mean_size) {
+      is_big[i] = true;
+      --rest_bins;
+      rest_cnt -= cnts[i];
+    }
+  }
+  mean_size = static_cast<double>(rest_cnt) / rest_bins;
+  std::vector<double> hi(max_bin, kInf), lo(max_bin, kInf);
+  int nb = 0;
+  lo[0] = vals[0];
+  int acc = 0;
+  for (int i = 0; i + 1 < n_distinct; ++i) {
+    if (!is_big[i]) rest_cnt -= cnts[i];
+    acc += cnts[i];
+    if (is_big[i] || acc >= mean_size || (is_big[i + 1] && acc >= std::max(1.0, mean_size * 0.5f))) {
+      hi[nb] = vals[i];
+      ++nb;
+      lo[nb] = vals[i + 1];
+      if (nb >= max_bin - 1) break;
+      acc = 0;
+      if (!is_big[i]) {
+        --rest_bins;
+        mean_size = rest_cnt / static_cast<double>(rest_bins);
+      }
+    }
+  }
+  ++nb;
+  for (int i = 0; i + 1 < nb; ++i) {
+    const double mid = NextUp((hi[i] + lo[i + 1]) / 2.0);
+    if (bounds.empty() || !EqualOrdered(bounds.back(), mid)) bounds.push_back(mid);
+  }
+  bounds.push_back(kInf);
+  return bounds;
+}
+
+// FindBinWithZeroAsOneBin (src/io/bin.cpp:256-312): negative side, the zero bin (-1e-35, 1e-35], positive side.
+std::vector<double> BoundsWithZeroBin(const double* vals, const int* cnts, int n_distinct, int max_bin,
+                                      size_t total_sample_cnt, int min_data_in_bin) {
+  std::vector<double> bounds;
+  int left_cnt_data = 0, cnt_zero = 0, right_cnt_data = 0;
+  for (int i = 0; i < n_distinct; ++i) {
+    if (vals[i] <= -kZeroThreshold) left_cnt_data += cnts[i];
+    else if (vals[i] > kZeroThreshold) right_cnt_data += cnts[i];
+    else cnt_zero += cnts[i];
+  }
+  int left_cnt = -1;
+  for (int i = 0; i < n_distinct; ++i) {
+    if (vals[i] > -kZeroThreshold) { left_cnt = i; break; }
+  }
+  if (left_cnt < 0) left_cnt = n_distinct;
+  if (left_cnt > 0 && max_bin > 1) {
+    int left_max_bin = static_cast<int>(static_cast<double>(left_cnt_data) / (total_sample_cnt - cnt_zero) * (max_bin - 1));
+    left_max_bin = std::max(1, left_max_bin);
+    bounds = GreedyBounds(vals, cnts, left_cnt, left_max_bin, left_cnt_data, min_data_in_bin);
+    if (!bounds.empty()) bounds.back() = -kZeroThreshold;
+  }
+  int right_start = -1;
+  for (int i = left_cnt; i < n_distinct; ++i) {
+    if (vals[i] > kZeroThreshold) { right_start = i; break; }
+  }
+  const int right_max_bin = max_bin - 1 - static_cast<int>(bounds.size());
+  if (right_start >= 0 && right_max_bin > 0) {
+    auto right = GreedyBounds(vals + right_start, cnts + right_start, n_distinct - right_start, right_max_bin,
+                              right_cnt_data, min_data_in_bin);
+    bounds.push_back(kZeroThreshold);
+    bounds.insert(bounds.end(), right.begin(), right.end());
+  } else {
+    bounds.push_back(kInf);
+  }
+  if (bounds.size() > static_cast<size_t>(max_bin)) Log::Fatal("Check failed: bin_upper_bound.size() <= max_bin");
+  return bounds;
+}
+
+// NeedFilter (src/io/bin.cpp:54-76), numerical branch: no split leaves >= filter_cnt rows on both sides
+bool NoUsefulSplit(const std::vector<int>& cnt_in_bin, int total_cnt, int filter_cnt) {
+  int left = 0;
+  for (size_t i = 0; i + 1 < cnt_in_bin.size(); ++i) {
+    left += cnt_in_bin[i];
+    if (left >= filter_cnt && total_cnt - left >= filter_cnt) return false;
+  }
+  return true;
+}
+
+}  // namespace
+
+void BinMapper::FindBin(std::vector<double> values, size_t total_sample_cnt, int max_bin, int min_data_in_bin,
+                        int min_split_data, bool pre_filter, bool use_missing, bool zero_as_missing) {
+  int num_sample = static_cast<int>(values.size());
+  // drop NaNs, remember how many
+  int kept = 0;
+  for (int i = 0; i < num_sample; ++i) if (!std::isnan(values[i])) values[kept++] = values[i];
+  int na_cnt = 0;
+  if (!use_missing) missing_type_ = kMissingNone;
+  else if (zero_as_missing) missing_type_ = kMissingZero;
+  else if (kept == num_sample) missing_type_ = kMissingNone;
+  else { missing_type_ = kMissingNaN; na_cnt = num_sample - kept; }
+  num_sample = kept;
+  values.resize(kept);
+  default_bin_ = 0;
+  const int zero_cnt = static_cast<int>(total_sample_cnt - num_sample - na_cnt);
+
+  std::stable_sort(values.begin(), values.end());
+  // distinct values with counts; the implied zeros are spliced in at their sorted position
+  std::vector<double> dv;
+  std::vector<int> dc;
+  if (num_sample == 0 || (values[0] > 0.0f && zero_cnt > 0)) { dv.push_back(0.0f); dc.push_back(zero_cnt); }
+  if (num_sample > 0) { dv.push_back(values[0]); dc.push_back(1); }
+  for (int i = 1; i < num_sample; ++i) {
+    if (!EqualOrdered(values[i - 1], values[i])) {
+      if (values[i - 1] < 0.0f && values[i] > 0.0f) { dv.push_back(0.0f); dc.push_back(zero_cnt); }
+      dv.push_back(values[i]);
+      dc.push_back(1);
+    } else {
+      dv.back() = values[i];  // keep the larger of two values one ulp apart
+      ++dc.back();
+    }
+  }
+  if (num_sample > 0 && values[num_sample - 1] < 0.0f && zero_cnt > 0) { dv.push_back(0.0f); dc.push_back(zero_cnt); }
+  min_val_ = dv.front();
+  max_val_ = dv.back();
+  const int nd = static_cast<int>(dv.size());
+
+  if (missing_type_ == kMissingZero) {
+    upper_ = BoundsWithZeroBin(dv.data(), dc.data(), nd, max_bin, total_sample_cnt, min_data_in_bin);
+    if (upper_.size() == 2) missing_type_ = kMissingNone;
+  } else if (missing_type_ == kMissingNone) {
+    upper_ = BoundsWithZeroBin(dv.data(), dc.data(), nd, max_bin, total_sample_cnt, min_data_in_bin);
+  } else {
+    upper_ = BoundsWithZeroBin(dv.data(), dc.data(), nd, max_bin - 1, total_sample_cnt - na_cnt, min_data_in_bin);
+    // src/io/bin.cpp:407 writes `bin_upper_bound_.push_back(NaN)` where `NaN` is the MissingType enumerator (= 2),
+    // so the reference's NaN bin carries the upper bound 2.0.  Never searched (ValueToBin stops one bin earlier)
+    // nor used as a threshold; kept identical so that mapper dumps compare equal.
+    upper_.push_back(static_cast<double>(kMissingNaN));
+  }
+  num_bin_ = static_cast<int>(upper_.size());
+  std::vector<int> cnt_in_bin(num_bin_, 0);
+  {
+    int b = 0;
+    for (int i = 0; i < nd; ++i) {
+      if (dv[i] > upper_[b]) ++b;
+      cnt_in_bin[b] += dc[i];
+    }
+    if (missing_type_ == kMissingNaN) cnt_in_bin[num_bin_ - 1] = na_cnt;
+  }
+  if (num_bin_ > max_bin) Log::Fatal("Check failed: (num_bin_) <= (max_bin)");
+
+  trivial_ = num_bin_ <= 1;
+  if (!trivial_ && pre_filter && NoUsefulSplit(cnt_in_bin, static_cast<int>(total_sample_cnt), min_split_data)) trivial_ = true;
+  if (!trivial_) {
+    default_bin_ = ValueToBin(0);
+    // ArrayArgs<int>::ArgMax: first maximum
+    most_freq_bin_ = static_cast<uint32_t>(std::max_element(cnt_in_bin.begin(), cnt_in_bin.end()) - cnt_in_bin.begin());
+    const double max_rate = static_cast<double>(cnt_in_bin[most_freq_bin_]) / total_sample_cnt;
+    if (most_freq_bin_ != default_bin_ && max_rate < kSparseThreshold) most_freq_bin_ = default_bin_;
+    sparse_rate_ = static_cast<double>(cnt_in_bin[most_freq_bin_]) / total_sample_cnt;
+  } else {
+    sparse_rate_ = 1.0f;
+  }
+}
+
+uint32_t BinMapper::ValueToBin(double value) const {
+  if (std::isnan(value)) {
+    if (missing_type_ == kMissingNaN) return num_bin_ - 1;
+    value = 0.0f;
+  }
+  int l = 0, r = num_bin_ - 1;
+  if (missing_type_ == kMissingNaN) r -= 1;
+  while (l < r) {
+    const int m = (r + l - 1) / 2;
+    if (value <= upper_[m]) r = m;
+    else l = m + 1;
+  }
+  return l;
+}
+
+std::string BinMapper::info_string() const {
+  std::ostringstream o;
+  o << std::setprecision(std::numeric_limits<double>::digits10 + 2) << '[' << min_val_ << ':' << max_val_ << ']';
+  return o.str();
+}
+
+}  // namespace lgb

@@ -1,0 +1,302 @@
+#include "dataset.h"
+
+#include <omp.h>
+
+#include <algorithm>
+#include <cstring>
+
+#include "random.h"
+
+namespace lgb {
+namespace {
+
+// RowFunctionFromDenseMatric (src/c_api.cpp:2296-2341): element accessor for f32/f64 x row/col-major
+struct MatView {
+  const void* data; int type; int32_t nrow, ncol; bool row_major;
+  double at(int32_t r, int32_t c) const {
+    const size_t i = row_major ? static_cast<size_t>(r) * ncol + c : static_cast<size_t>(c) * nrow + r;
+    return type == 0 ? static_cast<double>(static_cast<const float*>(data)[i]) : static_cast<const double*>(data)[i];
+  }
+};
+
+// ---- Exclusive-feature-bundling decision (src/io/dataset.cpp:50-313).  Only the grouping DECISION and the
+// resulting feature order are reproduced: this library stores every feature as its own group.  A bundle that
+// would share one column between several features (which may drop conflicting rows) is refused.
+int ConflictCount(const std::vector<bool>& mark, const std::vector<int>& idx, int max_cnt) {
+  int ret = 0;
+  for (int i : idx) {
+    if (mark[i]) ++ret;
+    if (ret > max_cnt) return -1;
+  }
+  return ret;
+}
+
+std::vector<std::vector<int>> FindGroups(const std::vector<std::shared_ptr<BinMapper>>& mappers,
+                                         const std::vector<int>& order, const std::vector<std::vector<int>>& nz_idx,
+                                         int total_sample_cnt, data_size_t num_data, bool is_sparse,
+                                         std::vector<int8_t>* multi_val) {
+  const int max_search_group = 100;
+  const int max_conflict = total_sample_cnt / 10000;
+  multi_val->clear();
+  Random rand(num_data);
+  std::vector<std::vector<int>> groups;
+  std::vector<std::vector<bool>> marks;
+  std::vector<int> used_rows, total_cnt, group_bins;
+  for (int f : order) {
+    const int nz = static_cast<int>(nz_idx[f].size());
+    std::vector<int> avail;
+    for (int g = 0; g < static_cast<int>(groups.size()); ++g) {
+      if (total_cnt[g] + nz <= total_sample_cnt + max_conflict) avail.push_back(g);
+    }
+    std::vector<int> search;
+    if (!avail.empty()) {
+      const int last = static_cast<int>(avail.size()) - 1;
+      auto pick = rand.Sample(last, std::min(last, max_search_group - 1));
+      search.push_back(avail.back());
+      for (int i : pick) search.push_back(avail[i]);
+    }
+    int best = -1, best_conf = -1;
+    for (int g : search) {
+      const int rest = max_conflict - total_cnt[g] + used_rows[g];
+      const int cnt = ConflictCount(marks[g], nz_idx[f], rest);
+      if (cnt >= 0 && cnt <= rest && cnt <= nz / 2) { best = g; best_conf = cnt; break; }
+    }
+    if (best >= 0) {
+      groups[best].push_back(f);
+      total_cnt[best] += nz;
+      used_rows[best] += nz - best_conf;
+      for (int i : nz_idx[f]) marks[best][i] = true;
+      group_bins[best] += mappers[f]->num_bin() + (mappers[f]->default_bin() == 0 ? -1 : 0);
+    } else {
+      groups.emplace_back(1, f);
+      marks.emplace_back(total_sample_cnt, false);
+      for (int i : nz_idx[f]) marks.back()[i] = true;
+      total_cnt.push_back(nz);
+      used_rows.push_back(nz);
+      group_bins.push_back(1 + mappers[f]->num_bin() + (mappers[f]->default_bin() == 0 ? -1 : 0));
+    }
+  }
+  if (!is_sparse) { multi_val->assign(groups.size(), 0); return groups; }
+  std::vector<int> second;
+  std::vector<std::vector<int>> groups2;
+  std::vector<std::vector<bool>> marks2;
+  for (size_t g = 0; g < groups.size(); ++g) {
+    const double dense_rate = static_cast<double>(used_rows[g]) / total_sample_cnt;
+    if (dense_rate >= 0.4) { groups2.push_back(std::move(groups[g])); marks2.push_back(std::move(marks[g])); }
+    else for (int f : groups[g]) second.push_back(f);
+  }
+  groups = groups2;
+  multi_val->assign(groups.size(), 0);
+  if (!second.empty()) {
+    groups.emplace_back();
+    std::vector<bool> mark(total_sample_cnt, false);
+    bool is_multi = false;
+    int conflicts = 0;
+    for (int f : second) {
+      groups.back().push_back(f);
+      if (!is_multi) {
+        const int rest = max_conflict - conflicts;
+        const int cnt = ConflictCount(mark, nz_idx[f], rest);
+        conflicts += cnt;
+        if (cnt < 0 || conflicts > max_conflict) { is_multi = true; continue; }
+        for (int i : nz_idx[f]) mark[i] = true;
+      }
+    }
+    multi_val->push_back(is_multi ? 1 : 0);
+  }
+  return groups;
+}
+
+// FastFeatureBundling (src/io/dataset.cpp:236-313) -> inner feature order
+std::vector<int> BundledFeatureOrder(const std::vector<std::shared_ptr<BinMapper>>& mappers,
+                                     const std::vector<int>& used, const std::vector<std::vector<double>>& sample_vals,
+                                     std::vector<std::vector<int>> sample_idx, int total_sample_cnt, data_size_t num_data) {
+  // FixSampleIndices: when the most frequent bin is not the zero bin, "non-zero" means "not in the most frequent bin"
+  for (int f : used) {
+    const BinMapper& m = *mappers[f];
+    if (m.default_bin() == m.most_freq_bin()) continue;
+    std::vector<int> fixed;
+    const auto& idx = sample_idx[f];
+    const auto& val = sample_vals[f];
+    int i = 0; size_t j = 0;
+    while (i < total_sample_cnt) {
+      if (j < idx.size() && idx[j] < i) ++j;
+      else if (j < idx.size() && idx[j] == i) {
+        if (m.ValueToBin(val[j]) != m.most_freq_bin()) fixed.push_back(i);
+        ++i;
+      } else fixed.push_back(i++);
+    }
+    // an empty result means "keep the original list" in the reference (it tests ret.empty())
+    if (!fixed.empty()) sample_idx[f] = fixed;
+  }
+  std::vector<int> by_cnt(used.size());
+  for (size_t i = 0; i < used.size(); ++i) by_cnt[i] = static_cast<int>(i);
+  // NOTE the reference sorts by the ORIGINAL non-zero counts (num_per_col), not the fixed ones; ordering only
+  // matters when it yields fewer groups, which for one-feature groups it never does.
+  std::vector<int8_t> mv1, mv2;
+  auto g1 = FindGroups(mappers, used, sample_idx, total_sample_cnt, num_data, true, &mv1);
+  std::vector<int> order2(used);
+  std::stable_sort(order2.begin(), order2.end(), [&](int a, int b) { return sample_vals[a].size() > sample_vals[b].size(); });
+  auto g2 = FindGroups(mappers, order2, sample_idx, total_sample_cnt, num_data, true, &mv2);
+  if (g1.size() > g2.size()) { g1 = g2; mv1 = mv2; }
+  const int ng = static_cast<int>(g1.size());
+  Random shuffle(num_data);
+  for (int i = 0; i < ng - 1; ++i) {
+    const int j = shuffle.NextShort(i + 1, ng);
+    std::swap(g1[i], g1[j]);
+    std::swap(mv1[i], mv1[j]);
+  }
+  std::vector<int> order;
+  for (int g = 0; g < ng; ++g) {
+    if (g1[g].size() > 1 && !mv1[g]) {
+      Log::Fatal("exclusive feature bundling would merge %d sparse features into one column; bundled groups are "
+                 "outside this library's path -- pass enable_bundle=false", static_cast<int>(g1[g].size()));
+    }
+    for (int f : g1[g]) order.push_back(f);
+  }
+  return order;
+}
+
+}  // namespace
+
+Dataset* Dataset::FromDenseMatrix(const void* data, int data_type, int32_t nrow, int32_t ncol, bool row_major,
+                                  const Config& config) {
+  if (nrow <= 0) Log::Fatal("Check failed: (num_data) > (0)");
+  if (data_type != 0 && data_type != 1) Log::Fatal("Unknown data type in RowFunctionFromDenseMatric");
+  const MatView M{data, data_type, nrow, ncol, row_major};
+  std::unique_ptr<Dataset> ds(new Dataset(nrow));
+  ds->num_total_features_ = ncol;
+  // sample rows (src/c_api.cpp:1045-1070)
+  Random rand(config.data_random_seed);
+  const int want = nrow < config.bin_construct_sample_cnt ? nrow : config.bin_construct_sample_cnt;
+  const std::vector<int> sample = rand.Sample(nrow, want);
+  const int sample_cnt = static_cast<int>(sample.size());
+  std::vector<std::vector<double>> sample_vals(ncol);
+  std::vector<std::vector<int>> sample_idx(ncol);
+  for (int i = 0; i < sample_cnt; ++i) {
+    for (int c = 0; c < ncol; ++c) {
+      const double v = M.at(sample[i], c);
+      if (std::fabs(v) > kZeroThreshold || std::isnan(v)) {
+        sample_vals[c].push_back(v);
+        sample_idx[c].push_back(i);
+      }
+    }
+  }
+  // bin mappers (DatasetLoader::ConstructFromSampleData, src/io/dataset_loader.cpp:527-585)
+  const data_size_t filter_cnt = static_cast<data_size_t>(static_cast<double>(config.min_data_in_leaf * static_cast<size_t>(sample_cnt)) / nrow);
+  std::vector<std::shared_ptr<BinMapper>> all(ncol);
+#pragma omp parallel for schedule(guided)
+  for (int c = 0; c < ncol; ++c) {
+    all[c].reset(new BinMapper());
+    all[c]->FindBin(sample_vals[c], static_cast<size_t>(sample_cnt), config.max_bin, config.min_data_in_bin, filter_cnt,
+                    config.feature_pre_filter, config.use_missing, config.zero_as_missing);
+  }
+  std::vector<int> used;
+  for (int c = 0; c < ncol; ++c) if (!all[c]->is_trivial()) used.push_back(c);
+  if (used.empty()) Log::Warning("There are no meaningful features, as all feature values are constant.");
+  std::vector<int> order = used;
+  if (config.enable_bundle && !used.empty()) {
+    order = BundledFeatureOrder(all, used, sample_vals, sample_idx, sample_cnt, nrow);
+  }
+  ds->real_to_inner_.assign(ncol, -1);
+  for (int f : order) {
+    if (all[f]->num_bin() + (all[f]->most_freq_bin() == 0 ? 0 : 1) > 256) {
+      Log::Fatal("feature %d needs more than 256 stored values; only 8-bit bins (max_bin <= 255) are built", f);
+    }
+    ds->real_to_inner_[f] = static_cast<int>(ds->inner_to_real_.size());
+    ds->inner_to_real_.push_back(f);
+    ds->mappers_.push_back(all[f]);
+  }
+  for (int c = 0; c < ncol; ++c) ds->feature_names_.push_back("Column_" + std::to_string(c));
+  ds->BinAllRows(data, data_type, nrow, ncol, row_major);
+  return ds.release();
+}
+
+Dataset* Dataset::FromDenseMatrixAligned(const void* data, int data_type, int32_t nrow, int32_t ncol, bool row_major,
+                                         const Dataset& ref) {
+  if (ncol != ref.num_total_features_) Log::Fatal("The number of features in data (%d) is not the same as it was in training data (%d).", ncol, ref.num_total_features_);
+  std::unique_ptr<Dataset> ds(new Dataset(nrow));
+  ds->num_total_features_ = ncol;
+  ds->mappers_ = ref.mappers_;
+  ds->inner_to_real_ = ref.inner_to_real_;
+  ds->real_to_inner_ = ref.real_to_inner_;
+  ds->feature_names_ = ref.feature_names_;
+  ds->BinAllRows(data, data_type, nrow, ncol, row_major);
+  return ds.release();
+}
+
+uint32_t Dataset::stored_value(int inner, double v) const {
+  const BinMapper& m = *mappers_[inner];
+  uint32_t bin = m.ValueToBin(v);
+  if (bin == m.most_freq_bin()) return 0;       // FeatureGroup::PushData (feature_group.h:153-165)
+  if (m.most_freq_bin() == 0) bin -= 1;
+  return bin + 1;
+}
+
+void Dataset::BinAllRows(const void* data, int data_type, int32_t nrow, int32_t ncol, bool row_major) {
+  const MatView M{data, data_type, nrow, ncol, row_major};
+  const int F = num_features();
+  bins_.assign(static_cast<size_t>(nrow) * std::max(F, 1), 0);
+#pragma omp parallel for schedule(static)
+  for (int32_t r = 0; r < nrow; ++r) {
+    uint8_t* out = bins_.data() + static_cast<size_t>(r) * F;
+    for (int f = 0; f < F; ++f) out[f] = static_cast<uint8_t>(stored_value(f, M.at(r, inner_to_real_[f])));
+  }
+}
+
+uint64_t Dataset::num_total_bin() const {
+  uint64_t t = 0;
+  for (auto& m : mappers_) t += 1 + m->num_bin() - (m->most_freq_bin() == 0 ? 1 : 0);
+  return t;
+}
+
+std::vector<std::string> Dataset::feature_infos() const {
+  std::vector<std::string> out;
+  for (int c = 0; c < num_total_features_; ++c) {
+    const int f = real_to_inner_[c];
+    out.push_back(f < 0 ? "none" : mappers_[f]->info_string());
+  }
+  return out;
+}
+
+// LGBM_DatasetSetField (src/c_api.cpp:1422-1439 -> Metadata::Set*)
+void Dataset::SetFloatField(const char* name, const float* data, int n) {
+  const std::string k(name);
+  if (k == "label" || k == "target") {
+    if (n != num_data_) Log::Fatal("Length of label is not same with #data");
+    meta_.label.assign(data, data + n);
+  } else if (k == "weight" || k == "weights") {
+    if (data == nullptr || n == 0) { meta_.weights.clear(); return; }
+    if (n != num_data_) Log::Fatal("Length of weights is not same with #data");
+    meta_.weights.assign(data, data + n);
+  } else {
+    Log::Fatal("Input field %s is not a float field", name);
+  }
+}
+
+void Dataset::SetDoubleField(const char* name, const double* data, int n) {
+  const std::string k(name);
+  if (k == "init_score") {
+    if (data == nullptr || n == 0) { meta_.init_score.clear(); return; }
+    if (n != num_data_) Log::Fatal("Initial score size doesn't match data size");
+    meta_.init_score.assign(data, data + n);
+  } else {
+    Log::Fatal("Input field %s is not a double field", name);
+  }
+}
+
+void Dataset::SetIntField(const char* name, const int32_t* data, int n) {
+  const std::string k(name);
+  if (k == "query" || k == "group") {
+    if (data == nullptr || n == 0) { meta_.query_boundaries.clear(); return; }
+    long long sum = 0;
+    for (int i = 0; i < n; ++i) sum += data[i];
+    if (sum != num_data_) Log::Fatal("Sum of query counts is not same with #data");
+    meta_.query_boundaries.assign(n + 1, 0);
+    for (int i = 0; i < n; ++i) meta_.query_boundaries[i + 1] = meta_.query_boundaries[i] + data[i];
+  } else {
+    Log::Fatal("Input field %s is not an int field", name);
+  }
+}
+
+}  // namespace lgb

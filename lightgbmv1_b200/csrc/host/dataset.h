@@ -1,0 +1,64 @@
+// Binned data store (A2): what Dataset / FeatureGroup / DenseBin / Metadata are to the reference's training path
+// (include/LightGBM/dataset.h, feature_group.h; src/io/dataset.cpp:315-432; src/c_api.cpp:1018-1100).
+// Host side keeps the bin mappers, the feature order and a row-major u8 matrix of stored values that the CUDA
+// learner uploads once; one feature per group (dense data), stored value = the reference's single-feature
+// group encoding.
+#pragma once
+#include <memory>
+#include <string>
+#include <vector>
+
+#include "bin_mapper.h"
+#include "config.h"
+
+namespace lgb {
+
+struct Metadata {
+  std::vector<label_t> label;
+  std::vector<label_t> weights;
+  std::vector<data_size_t> query_boundaries;  // num_queries + 1, empty if none
+  std::vector<double> init_score;
+};
+
+class Dataset {
+ public:
+  // LGBM_DatasetCreateFromMat with reference == nullptr: sample, find bins, bin every row
+  static Dataset* FromDenseMatrix(const void* data, int data_type, int32_t nrow, int32_t ncol, bool row_major,
+                                  const Config& config);
+  // ... with a reference dataset: reuse its mappers and feature order (Dataset::CreateValid)
+  static Dataset* FromDenseMatrixAligned(const void* data, int data_type, int32_t nrow, int32_t ncol, bool row_major,
+                                         const Dataset& reference);
+
+  data_size_t num_data() const { return num_data_; }
+  int num_features() const { return static_cast<int>(inner_to_real_.size()); }
+  int num_total_features() const { return num_total_features_; }
+  int real_feature_index(int inner) const { return inner_to_real_[inner]; }
+  int inner_feature_index(int real) const { return real_to_inner_[real]; }
+  const BinMapper& mapper(int inner) const { return *mappers_[inner]; }
+  const std::vector<uint8_t>& bins() const { return bins_; }  // row-major [num_data][num_features]
+  uint64_t num_total_bin() const;
+  Metadata& metadata() { return meta_; }
+  const Metadata& metadata() const { return meta_; }
+  const std::vector<std::string>& feature_names() const { return feature_names_; }
+  std::vector<std::string> feature_infos() const;
+  // value of feature `real` in bin space for one raw value (used by prediction on binned data)
+  uint32_t stored_value(int inner, double v) const;
+
+  void SetFloatField(const char* name, const float* data, int n);
+  void SetDoubleField(const char* name, const double* data, int n);
+  void SetIntField(const char* name, const int32_t* data, int n);
+
+ private:
+  explicit Dataset(data_size_t n) : num_data_(n) {}
+  void BinAllRows(const void* data, int data_type, int32_t nrow, int32_t ncol, bool row_major);
+
+  data_size_t num_data_;
+  int num_total_features_ = 0;
+  std::vector<std::shared_ptr<BinMapper>> mappers_;  // per inner feature
+  std::vector<int> inner_to_real_, real_to_inner_;
+  std::vector<uint8_t> bins_;
+  std::vector<std::string> feature_names_;
+  Metadata meta_;
+};
+
+}  // namespace lgb

@@ -1,0 +1,71 @@
+// Boosting driver for the CUDA learner: the part of GBDT (src/boosting/gbdt.cpp:42-119,151-160,209-243,312-419,
+// 458-478,739-797) that calls the hot path, with gradients, scores, partition and histograms resident on the
+// device.  The host keeps the O(num_leaves) Tree objects, the bagging / column-sampling random streams and the
+// model text.
+#pragma once
+#include <memory>
+#include <string>
+#include <vector>
+
+#include "config.h"
+#include "dataset.h"
+#include "lgbcu.h"
+#include "objective.h"
+#include "random.h"
+#include "tree.h"
+
+namespace lgb {
+
+// process-wide (thread-local, like the reference's Network statics, src/network/network.cpp:17-27) NCCL rendezvous
+struct NetworkState {
+  bool active = false;
+  uint8_t unique_id[128];
+  int rank = 0, num_machines = 1;
+};
+NetworkState& Net();
+
+class GBDT {
+ public:
+  GBDT(const Dataset* train, const Config& config);
+  ~GBDT();
+  bool TrainOneIter(const float* grad, const float* hess);  // true = finished (cannot split any more)
+  int current_iteration() const { return static_cast<int>(models_.size()); }
+  int num_data() const { return train_->num_data(); }
+  void GetTrainScore(double* out, bool converted) const;      // LGBM_BoosterGetPredict(data_idx = 0)
+  void PredictMat(const void* data, int data_type, int32_t nrow, int32_t ncol, bool row_major, bool raw_score,
+                  int num_iteration, double* out) const;
+  std::string SaveModelToString(int start_iteration, int num_iteration) const;
+  const Config& config() const { return config_; }
+  LgbCuContext* device() const { return ctx_; }
+  int64_t total_device_launches() const;
+
+ private:
+  void Bagging(int iter);
+  void ResetFeatureMask();
+  std::vector<double> FeatureImportanceSplit(int num_iteration) const;
+
+  const Dataset* train_;
+  Config config_;
+  std::unique_ptr<Objective> objective_;
+  LgbCuContext* ctx_ = nullptr;
+  std::vector<std::unique_ptr<Tree>> models_;
+  int iter_ = 0;
+  double shrinkage_rate_;
+  bool has_init_score_ = false;
+  bool class_need_train_ = true;
+  // bagging (gbdt.cpp:209-243, 739-797)
+  std::vector<data_size_t> bag_indices_;  // in-bag (ascending) then out-of-bag (ascending)
+  data_size_t bag_cnt_;
+  std::vector<Random> bagging_rands_;
+  bool need_re_bagging_ = false;
+  int64_t bag_version_ = 0;
+  // column sampling (col_sampler.hpp)
+  Random feature_rand_;
+  std::vector<int> valid_features_;  // real indices of used features
+  std::vector<int8_t> feature_used_;
+  int used_cnt_bytree_ = 0;
+  bool need_reset_bytree_ = false;
+  std::vector<LgbCuSplitRecord> records_;
+};
+
+}  // namespace lgb

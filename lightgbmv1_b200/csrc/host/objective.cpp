@@ -1,0 +1,124 @@
+#include "objective.h"
+
+#include <cmath>
+
+namespace lgb {
+namespace {
+
+void Check(int rc) {
+  if (rc != 0) Log::Fatal("%s", lgbcu_last_error());
+}
+
+// src/objective/binary_objective.hpp
+class BinaryLogloss : public Objective {
+ public:
+  explicit BinaryLogloss(const Config& c) : sigmoid_(c.sigmoid), is_unbalance_(c.is_unbalance), scale_pos_weight_(c.scale_pos_weight) {
+    if (sigmoid_ <= 0.0) Log::Fatal("Sigmoid parameter %f should be greater than zero", sigmoid_);
+    if (is_unbalance_ && std::fabs(scale_pos_weight_ - 1.0f) > 1e-6) Log::Fatal("Cannot set is_unbalance and scale_pos_weight at the same time");
+  }
+  void Init(const Metadata& meta, data_size_t n) override {
+    num_data_ = n; label_ = meta.label.data(); weights_ = meta.weights.empty() ? nullptr : meta.weights.data();
+    if (meta.label.empty()) Log::Fatal("Label should not be NULL");
+    data_size_t pos = 0, neg = 0;
+    for (data_size_t i = 0; i < n; ++i) { if (label_[i] > 0) ++pos; else ++neg; }
+    need_train_ = !(neg == 0 || pos == 0);
+    if (!need_train_) Log::Warning("Contains only one class");
+    Log::Info("Number of positive: %d, number of negative: %d", pos, neg);
+    label_weights_[0] = label_weights_[1] = 1.0f;
+    if (is_unbalance_ && pos > 0 && neg > 0) {
+      if (pos > neg) { label_weights_[1] = 1.0f; label_weights_[0] = static_cast<double>(pos) / neg; }
+      else { label_weights_[1] = static_cast<double>(neg) / pos; label_weights_[0] = 1.0f; }
+    }
+    label_weights_[1] *= scale_pos_weight_;
+  }
+  void Configure(LgbCuContext* ctx) const override {
+    Check(lgbcu_set_objective(ctx, LGBCU_OBJ_BINARY, sigmoid_, label_weights_[0], label_weights_[1]));
+  }
+  double BoostFromScore() const override {
+    double suml = 0.0f, sumw = 0.0f;
+    if (weights_) {
+      for (data_size_t i = 0; i < num_data_; ++i) { suml += (label_[i] > 0) * weights_[i]; sumw += weights_[i]; }
+    } else {
+      sumw = static_cast<double>(num_data_);
+      for (data_size_t i = 0; i < num_data_; ++i) suml += (label_[i] > 0);
+    }
+    double pavg = suml / sumw;
+    pavg = std::min(pavg, 1.0 - kEpsilon);
+    pavg = std::max<double>(pavg, kEpsilon);
+    const double init = std::log(pavg / (1.0f - pavg)) / sigmoid_;
+    Log::Info("[binary:BoostFromScore]: pavg=%f -> initscore=%f", pavg, init);
+    return init;
+  }
+  bool NeedTrain() const override { return need_train_; }
+  void ConvertOutput(const double* in, double* out) const override { out[0] = 1.0f / (1.0f + std::exp(-sigmoid_ * in[0])); }
+  std::string ToString() const override { std::ostringstream o; o << "binary sigmoid:" << sigmoid_; return o.str(); }
+  const char* Name() const override { return "binary"; }
+
+ private:
+  double sigmoid_; bool is_unbalance_; double scale_pos_weight_;
+  data_size_t num_data_ = 0; const label_t* label_ = nullptr; const label_t* weights_ = nullptr;
+  bool need_train_ = true; double label_weights_[2] = {1, 1};
+};
+
+// src/objective/regression_objective.hpp (RegressionL2loss)
+class RegressionL2 : public Objective {
+ public:
+  explicit RegressionL2(const Config& c) {
+    if (c.reg_sqrt) Log::Fatal("reg_sqrt is outside this library's path");
+  }
+  void Init(const Metadata& meta, data_size_t n) override {
+    num_data_ = n; label_ = meta.label.data(); weights_ = meta.weights.empty() ? nullptr : meta.weights.data();
+    if (meta.label.empty()) Log::Fatal("Label should not be NULL");
+  }
+  void Configure(LgbCuContext* ctx) const override { Check(lgbcu_set_objective(ctx, LGBCU_OBJ_L2, 0, 0, 0)); }
+  double BoostFromScore() const override {
+    double suml = 0.0f, sumw = 0.0f;
+    if (weights_) {
+      for (data_size_t i = 0; i < num_data_; ++i) { suml += label_[i] * weights_[i]; sumw += weights_[i]; }
+    } else {
+      sumw = static_cast<double>(num_data_);
+      for (data_size_t i = 0; i < num_data_; ++i) suml += label_[i];
+    }
+    return suml / sumw;
+  }
+  bool IsConstantHessian() const override { return weights_ == nullptr; }
+  std::string ToString() const override { return "regression"; }
+  const char* Name() const override { return "regression"; }
+
+ private:
+  data_size_t num_data_ = 0; const label_t* label_ = nullptr; const label_t* weights_ = nullptr;
+};
+
+// src/objective/rank_objective.hpp (LambdarankNDCG); label checks / max DCG / sigmoid table happen in lgbcu
+class Lambdarank : public Objective {
+ public:
+  explicit Lambdarank(const Config& c)
+      : sigmoid_(c.sigmoid), norm_(c.lambdarank_norm), trunc_(c.lambdarank_truncation_level), label_gain_(c.label_gain) {
+    if (sigmoid_ <= 0.0) Log::Fatal("Sigmoid param %f should be greater than zero", sigmoid_);
+  }
+  void Init(const Metadata& meta, data_size_t) override {
+    if (meta.query_boundaries.empty()) Log::Fatal("Ranking tasks require query information");
+  }
+  void Configure(LgbCuContext* ctx) const override {
+    Check(lgbcu_set_objective(ctx, LGBCU_OBJ_LAMBDARANK, sigmoid_, trunc_, norm_ ? 1 : 0));
+    if (!label_gain_.empty()) Check(lgbcu_set_label_gain(ctx, label_gain_.data(), static_cast<int>(label_gain_.size())));
+  }
+  double BoostFromScore() const override { return 0.0; }
+  std::string ToString() const override { return "lambdarank"; }
+  const char* Name() const override { return "lambdarank"; }
+
+ private:
+  double sigmoid_; bool norm_; int trunc_; std::vector<double> label_gain_;
+};
+
+}  // namespace
+
+Objective* Objective::Create(const Config& c) {
+  if (c.objective == "binary") return new BinaryLogloss(c);
+  if (c.objective == "regression") return new RegressionL2(c);
+  if (c.objective == "lambdarank") return new Lambdarank(c);
+  if (c.objective == "custom") return nullptr;
+  Log::Fatal("objective=%s is outside this library's path (binary, regression/l2, lambdarank, custom)", c.objective.c_str());
+}
+
+}  // namespace lgb

@@ -1,0 +1,29 @@
+// Host half of the objectives north_star names: everything ObjectiveFunction::Init / BoostFromScore /
+// ConvertOutput / ToString do in the reference (src/objective/binary_objective.hpp:56-158,
+// regression_objective.hpp:93-199, rank_objective.hpp:100-140).  GetGradients itself runs on device
+// (lgbcu_get_gradients); this class only derives its parameters.
+#pragma once
+#include <memory>
+#include <string>
+
+#include "config.h"
+#include "dataset.h"
+#include "lgbcu.h"
+
+namespace lgb {
+
+class Objective {
+ public:
+  static Objective* Create(const Config& config);  // ObjectiveFunction::CreateObjectiveFunction
+  virtual ~Objective() {}
+  virtual void Init(const Metadata& meta, data_size_t num_data) = 0;
+  virtual void Configure(LgbCuContext* ctx) const = 0;  // push kind + parameters to the device learner
+  virtual double BoostFromScore() const = 0;
+  virtual bool NeedTrain() const { return true; }
+  virtual bool IsConstantHessian() const { return false; }
+  virtual void ConvertOutput(const double* in, double* out) const { out[0] = in[0]; }
+  virtual std::string ToString() const = 0;
+  virtual const char* Name() const = 0;
+};
+
+}  // namespace lgb

@@ -1,0 +1,117 @@
+#include "tree.h"
+
+namespace lgb {
+
+static inline double MaybeRoundToZero(double v) { return (v >= -kZeroThreshold && v <= kZeroThreshold) ? 0 : v; }
+
+Tree::Tree(int max_leaves) : max_leaves_(max_leaves), num_leaves_(1), shrinkage_(1.0f) {
+  const int n = std::max(max_leaves, 2);
+  left_child_.resize(n - 1); right_child_.resize(n - 1);
+  split_feature_inner_.resize(n - 1); split_feature_.resize(n - 1);
+  threshold_in_bin_.resize(n - 1); threshold_.resize(n - 1);
+  decision_type_.assign(n - 1, 0); split_gain_.resize(n - 1);
+  leaf_parent_.resize(n); leaf_value_.resize(n); leaf_weight_.resize(n); leaf_count_.resize(n);
+  internal_value_.resize(n - 1); internal_weight_.resize(n - 1); internal_count_.resize(n - 1);
+  leaf_depth_.resize(n);
+  leaf_depth_[0] = 0; leaf_value_[0] = 0.0f; leaf_weight_[0] = 0.0f; leaf_parent_[0] = -1;
+}
+
+int Tree::Split(int leaf, int feature_inner, int feature_real, uint32_t threshold_bin, double threshold_double,
+                double left_value, double right_value, int left_cnt, int right_cnt, double left_weight,
+                double right_weight, float gain, int missing_type, bool default_left) {
+  const int node = num_leaves_ - 1;
+  const int parent = leaf_parent_[leaf];
+  if (parent >= 0) {
+    if (left_child_[parent] == ~leaf) left_child_[parent] = node;
+    else right_child_[parent] = node;
+  }
+  split_feature_inner_[node] = feature_inner;
+  split_feature_[node] = feature_real;
+  split_gain_[node] = gain;
+  left_child_[node] = ~leaf;
+  right_child_[node] = ~num_leaves_;
+  leaf_parent_[leaf] = node;
+  leaf_parent_[num_leaves_] = node;
+  internal_weight_[node] = leaf_weight_[leaf];
+  internal_value_[node] = leaf_value_[leaf];
+  internal_count_[node] = left_cnt + right_cnt;
+  leaf_value_[leaf] = std::isnan(left_value) ? 0.0f : left_value;
+  leaf_weight_[leaf] = left_weight;
+  leaf_count_[leaf] = left_cnt;
+  leaf_value_[num_leaves_] = std::isnan(right_value) ? 0.0f : right_value;
+  leaf_weight_[num_leaves_] = right_weight;
+  leaf_count_[num_leaves_] = right_cnt;
+  leaf_depth_[num_leaves_] = leaf_depth_[leaf] + 1;
+  leaf_depth_[leaf]++;
+  // decision_type: bit0 categorical, bit1 default_left, bits 2-3 missing type (tree.h SetMissingType)
+  int8_t dt = 0;
+  if (default_left) dt |= kDefaultLeftMask;
+  dt = static_cast<int8_t>((dt & 3) | (missing_type << 2));
+  decision_type_[node] = dt;
+  threshold_in_bin_[node] = threshold_bin;
+  threshold_[node] = threshold_double;
+  ++num_leaves_;
+  return num_leaves_ - 1;
+}
+
+void Tree::Shrinkage(double rate) {
+  for (int i = 0; i < num_leaves_ - 1; ++i) {
+    leaf_value_[i] = MaybeRoundToZero(leaf_value_[i] * rate);
+    internal_value_[i] = MaybeRoundToZero(internal_value_[i] * rate);
+  }
+  leaf_value_[num_leaves_ - 1] = MaybeRoundToZero(leaf_value_[num_leaves_ - 1] * rate);
+  shrinkage_ *= rate;
+}
+
+void Tree::AddBias(double val) {
+  for (int i = 0; i < num_leaves_ - 1; ++i) {
+    leaf_value_[i] = MaybeRoundToZero(leaf_value_[i] + val);
+    internal_value_[i] = MaybeRoundToZero(internal_value_[i] + val);
+  }
+  leaf_value_[num_leaves_ - 1] = MaybeRoundToZero(leaf_value_[num_leaves_ - 1] + val);
+  shrinkage_ = 1.0f;
+}
+
+std::string Tree::ToString() const {
+  std::ostringstream o;
+  const size_t ni = static_cast<size_t>(num_leaves_ - 1), nl = static_cast<size_t>(num_leaves_);
+  std::vector<int> dt(decision_type_.begin(), decision_type_.end());
+  o << "num_leaves=" << num_leaves_ << '\n';
+  o << "num_cat=" << 0 << '\n';
+  o << "split_feature=" << JoinInts(split_feature_, ni) << '\n';
+  o << "split_gain=" << JoinG(split_gain_, ni) << '\n';
+  o << "threshold=" << Join17(threshold_, ni) << '\n';
+  o << "decision_type=" << JoinInts(dt, ni) << '\n';
+  o << "left_child=" << JoinInts(left_child_, ni) << '\n';
+  o << "right_child=" << JoinInts(right_child_, ni) << '\n';
+  o << "leaf_value=" << Join17(leaf_value_, nl) << '\n';
+  o << "leaf_weight=" << Join17(leaf_weight_, nl) << '\n';
+  o << "leaf_count=" << JoinInts(leaf_count_, nl) << '\n';
+  o << "internal_value=" << JoinG(internal_value_, ni) << '\n';
+  o << "internal_weight=" << JoinG(internal_weight_, ni) << '\n';
+  o << "internal_count=" << JoinInts(internal_count_, ni) << '\n';
+  o << "shrinkage=" << shrinkage_ << '\n';
+  o << '\n';
+  return o.str();
+}
+
+// Tree::Predict -> GetLeaf -> NumericalDecision (include/LightGBM/tree.h:250-283)
+double Tree::Predict(const double* x) const {
+  if (num_leaves_ <= 1) return leaf_value_[0];
+  int node = 0;
+  while (node >= 0) {
+    double fval = x[split_feature_[node]];
+    const int missing_type = (decision_type_[node] >> 2) & 3;
+    const bool default_left = (decision_type_[node] & kDefaultLeftMask) != 0;
+    if (std::isnan(fval) && missing_type != kMissingNaN) fval = 0.0f;
+    if ((missing_type == kMissingZero && (fval >= -kZeroThreshold && fval <= kZeroThreshold)) ||
+        (missing_type == kMissingNaN && std::isnan(fval))) {
+      node = default_left ? left_child_[node] : right_child_[node];
+    } else {
+      node = fval <= threshold_[node] ? left_child_[node] : right_child_[node];
+    }
+  }
+  return leaf_value_[~node];
+}
+
+}  // namespace lgb

@@ -274,7 +274,10 @@ static void reset_split(LgbCuSplitInfo* s) {
   s->feature = -1; s->real_feature = -1; s->gain = K_MIN_SCORE; s->default_left = 1;
 }
 
-/* serial_tree_learner.cpp:358-425 + :701-736 for one leaf whose histogram still needs FixHistogram */
+/* serial_tree_learner.cpp:358-425 + :701-736 for one leaf whose histogram still needs FixHistogram.
+ * is_root: the reference's test is `leaf_splits->leaf_index() == 0` (:710) -- true for the root AND for every later
+ * leaf that still carries id 0 (the left child keeps its parent's id), whose "parent output" is therefore its own
+ * unsmoothed output instead of the output its parent's split assigned.  Only matters with path_smooth. */
 void orc_find_best_split(double* hist, const LgbCuFeatureMeta* feats, int num_features, const int8_t* feature_used,
                          const LgbCuTreeParams* p, double sum_g, double sum_h, int num_data, int is_root,
                          double leaf_out, LgbCuSplitInfo* out, int8_t* splittable) {
@@ -422,7 +425,7 @@ int orc_train_tree(const uint8_t* bins, int num_rows_total, int num_features, co
       {
         int8_t* spt = (int8_t*)calloc((size_t)num_features, 1);
         orc_find_best_split(hs, feats, num_features, used, p, leaves[smaller].sum_g, leaves[smaller].sum_h,
-                            leaves[smaller].count, smaller == 0 && right_leaf < 0, leaves[smaller].output, &best[smaller], spt);
+                            leaves[smaller].count, smaller == 0, leaves[smaller].output, &best[smaller], spt);
         for (int f = 0; f < num_features; ++f) if (used[f]) sp_s[f] = spt[f];
         free(spt);
       }
@@ -430,7 +433,6 @@ int orc_train_tree(const uint8_t* bins, int num_rows_total, int num_features, co
         double* hl = pool + (size_t)leaves[larger].slot * 2 * total_bin;
         int8_t* sp_l = splittable + (size_t)leaves[larger].slot * num_features;
         const Flags fl = make_flags(p);
-        (void)fl;
         LgbCuSplitInfo bl; reset_split(&bl);
         int base = 0;
         for (int f = 0; f < num_features; ++f) {
@@ -442,8 +444,13 @@ int orc_train_tree(const uint8_t* bins, int num_rows_total, int num_features, co
           const int cnt = (feats[f].num_bin - feat_offset(&feats[f])) * 2;
           for (int i = 0; i < cnt; ++i) dl[i] -= ds[i];  /* FeatureHistogram::Subtract */
           LgbCuSplitInfo s; int sp = 0;
+          double parent_output = leaves[larger].output;
+          if (larger == 0) {  /* ComputeBestSplitForFeature tests leaf_index() == 0, not "is the root" (see below) */
+            Flags f0 = fl; f0.use_smoothing = 0;
+            parent_output = leaf_output(leaves[larger].sum_g, leaves[larger].sum_h, p, f0, leaves[larger].count, 0);
+          }
           orc_find_best_threshold(dl, &feats[f], p, leaves[larger].sum_g, leaves[larger].sum_h, leaves[larger].count,
-                                  leaves[larger].output, &s, &sp);
+                                  parent_output, &s, &sp);
           s.feature = f; s.real_feature = feats[f].real_index;
           sp_l[f] = (int8_t)sp;
           if (split_greater(&s, &bl)) bl = s;
