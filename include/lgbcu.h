@@ -200,6 +200,28 @@ LGBCU_API int lgbcu_comm_destroy(LgbCuContext* ctx);
  * 160-260): in-place sum over ranks of n <= 64 doubles.  No-op on one rank. */
 LGBCU_API int lgbcu_comm_allreduce_sum_f64(LgbCuContext* ctx, double* inout, int32_t n);
 
+/* No counterpart in the reference (its DataPartition::Split allocates its own buffers on the host).
+ * A stable two-way partition of `n` row indices by one feature column that allocates NOTHING: for callers that own
+ * their input/output buffers but may not obtain device memory when they need the partition (a host running under
+ * someone else's fixed GPU memory arena, or a latency path that cannot afford cudaMalloc's device-wide sync).
+ * The kernel's working memory is a fixed array inside this library: every GPU that loads the library holds about
+ * 0.53 MB for it until exit, and one call handles at most LGBCU_NOALLOC_MAX_ROWS = 4,194,304 rows (more is
+ * refused with an error).  All pointers except `meta` are DEVICE pointers owned by the caller:
+ *   bins_dev        row-major u8 matrix, `row_stride` bytes per row; `column` = byte of the split feature
+ *   meta            (host) bin-mapper facts of that feature, as for lgbcu_set_dataset
+ *   indices_in_dev  n row indices; indices_out_dev (a different buffer) receives the rows going left, in their
+ *                   original order, followed by the rows going right, in their original order
+ *   left_count_dev  one int32 on the device: number of rows that went left
+ *   stream          cudaStream_t (NULL = default stream); the call only enqueues kernels and returns
+ * Same decision rule as lgbcu_partition / DenseBin::SplitInner.  Calls share the built-in array: calls that can
+ * overlap on one GPU race -- keep them on one stream.  The first call on a device resolves the array's address;
+ * make it before any stream capture begins. */
+#define LGBCU_NOALLOC_MAX_ROWS (1 << 22)
+LGBCU_API int lgbcu_partition_rows_noalloc(const uint8_t* bins_dev, int64_t row_stride, int32_t column,
+                                           const LgbCuFeatureMeta* meta, int32_t threshold, int32_t default_left,
+                                           const int32_t* indices_in_dev, int32_t n, int32_t* indices_out_dev,
+                                           int32_t* left_count_dev, void* stream);
+
 /* instrumentation for bench.py: device-time (ms, CUDA events on the context's stream) spent in the histogram
  * kernel since the last reset, its launch count and the algorithmic bytes it processed
  * (n*(G+8) [+4n if indexed] + total_bin*16 per call). */

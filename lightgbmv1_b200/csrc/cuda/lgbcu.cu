@@ -819,3 +819,5 @@ int lgbcu_comm_destroy(LgbCuContext* c) {
 }
 
 }  // extern "C"
+
+#include "noalloc_partition.cuh"
