@@ -85,6 +85,8 @@ struct DevView {
   const DevFeat* feats;
   const int8_t* feat_used;   // ColSampler by-tree mask
   int8_t* splittable;        // [num_leaves slots][num_features]  FeatureHistogram::is_splittable_
+  int8_t* parent_split;      // [num_features] the split leaf's flags, snapshotted by k_part_scan for both children
+  double2* mfb_fix;          // [num_leaves slots][num_features] FixHistogram'd most-frequent-bin entry, in double
   float* grad; float* hess;
   int* indices[2];
   HistEntry* pool;           // [num_leaves][total_bin]

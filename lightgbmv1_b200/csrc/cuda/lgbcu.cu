@@ -94,7 +94,7 @@ struct LgbCuContext {
   DevParams params{}; bool params_set = false;
   int alloc_leaves = 0;
   HistEntry* d_pool = nullptr;
-  int8_t* d_splittable = nullptr;
+  int8_t* d_splittable = nullptr; int8_t* d_parent_split = nullptr; double2* d_mfb_fix = nullptr;
   DevLeaf* d_leaves = nullptr;
   DevSplit *d_best = nullptr, *d_feat_best = nullptr;
   DevCtl* d_ctl = nullptr;
@@ -123,6 +123,7 @@ struct LgbCuContext {
     DevView V;
     V.num_data = N; V.num_features = F; V.row_stride = stride; V.total_bin = total_bin; V.num_tiles16 = ntiles16;
     V.bins = d_bins; V.feats = d_feats; V.feat_used = d_feat_used; V.splittable = d_splittable;
+    V.parent_split = d_parent_split; V.mfb_fix = d_mfb_fix;
     V.grad = d_grad; V.hess = d_hess; V.indices[0] = d_indices[0]; V.indices[1] = d_indices[1];
     V.pool = d_pool; V.leaves = d_leaves; V.best = d_best; V.feat_best = d_feat_best; V.ctl = d_ctl;
     V.records = d_records; V.tile_left = d_tile_left; V.part_bits = d_part_bits; V.p = params;
@@ -149,6 +150,8 @@ int ensure_tree_buffers(LgbCuContext* c) {
   CU(cudaSetDevice(c->device));
   CU(dev_alloc(&c->d_pool, (size_t)L * c->total_bin));
   CU(dev_alloc(&c->d_splittable, (size_t)L * c->F));
+  CU(dev_alloc(&c->d_mfb_fix, (size_t)L * c->F));
+  CU(cudaMemsetAsync(c->d_mfb_fix, 0, sizeof(double2) * (size_t)L * c->F, c->stream));
   CU(dev_alloc(&c->d_leaves, (size_t)L));
   CU(dev_alloc(&c->d_best, (size_t)L));
   CU(dev_alloc(&c->d_records, (size_t)L));
@@ -254,7 +257,7 @@ int lgbcu_destroy(LgbCuContext* c) {
                   c->d_indices[0], c->d_indices[1], c->d_part_bits, c->d_tile_left, c->d_query, c->d_label_gain,
                   c->d_inv_max_dcg, c->d_sigmoid_table, c->d_pool, c->d_splittable, c->d_leaves, c->d_best,
                   c->d_feat_best, c->d_ctl, c->d_records, c->d_leaf_value, c->d_export, c->d_tree_i32, c->d_tree_i8,
-                  c->d_tree_f64, c->d_rows, c->d_scratch};
+                  c->d_tree_f64, c->d_rows, c->d_scratch, c->d_parent_split, c->d_mfb_fix};
   for (void* p : ptrs) if (p) cudaFree(p);
   if (c->h_records) cudaFreeHost(c->h_records);
   if (c->h_ctl) cudaFreeHost(c->h_ctl);
@@ -300,6 +303,8 @@ static int setup_dataset_common(LgbCuContext* c, int32_t num_data, int32_t num_f
   CU(dev_alloc(&c->d_feat_used, (size_t)num_features));
   CU(cudaMemsetAsync(c->d_feat_used, 1, num_features, c->stream));
   CU(dev_alloc(&c->d_feat_best, (size_t)2 * num_features));
+  CU(dev_alloc(&c->d_parent_split, (size_t)num_features));
+  CU(cudaMemsetAsync(c->d_parent_split, 1, num_features, c->stream));
   CU(dev_alloc(&c->d_grad, (size_t)num_data));
   CU(dev_alloc(&c->d_hess, (size_t)num_data));
   CU(dev_alloc(&c->d_score, (size_t)num_data));
@@ -638,7 +643,7 @@ int lgbcu_find_best_split(LgbCuContext* c, int32_t leaf, LgbCuSplitInfo* out) {
   NEED(c && out && c->tree_begun, "lgbcu_find_best_split: bad argument / no tree begun");
   NEED(leaf >= 0 && leaf < c->params.num_leaves, "lgbcu_find_best_split: leaf %d out of range", leaf);
   CU(cudaSetDevice(c->device));
-  LAUNCH(k_find_split, c->F, 64, 0, c->stream, c->view(), 1, leaf);
+  LAUNCH(k_find_split, dim3(c->F, 1), FS_THREADS, 0, c->stream, c->view(), 1, leaf);
   CU(cudaGetLastError());
   CU(cudaMemcpyAsync(c->h_split, c->d_best + leaf, sizeof(DevSplit), cudaMemcpyDeviceToHost, c->stream));
   CU(cudaStreamSynchronize(c->stream));
@@ -728,7 +733,7 @@ int lgbcu_train_tree(LgbCuContext* c, LgbCuSplitRecord* records, int32_t* num_sp
     if (prof) CU(cudaEventRecord(c->ev[2 * s + 1], c->stream));
     if (comm_reduce_hist(c, s)) return -1;
     if (s == 0) LAUNCH(k_root_sums, 1, 32, 0, c->stream, V);
-    LAUNCH(k_find_split, c->F, 64, 0, c->stream, V, 0, -1);
+    LAUNCH(k_find_split, dim3(c->F, 2), FS_THREADS, 0, c->stream, V, 0, -1);
     LAUNCH(k_part_flags, part_grid, PART_THREADS, 0, c->stream, V);
     LAUNCH(k_part_scan, 1, 1024, 0, c->stream, V, 0);
     LAUNCH(k_part_scatter, part_grid, PART_THREADS, 0, c->stream, V, 0);

@@ -108,6 +108,10 @@ __global__ void __launch_bounds__(1024) k_part_scan(DevView V, int mode) {
   const int leaf = c->split_leaf;
   const DevLeaf L = V.leaves[leaf];
   const int ntiles = (L.count + PART_TILE - 1) / PART_TILE;
+  if (mode == 0) {  // snapshot FeatureHistogram::is_splittable_ of the leaf being split for k_find_split
+    const int8_t* src = V.splittable + (size_t)L.slot * V.num_features;
+    for (int f = threadIdx.x; f < V.num_features; f += blockDim.x) V.parent_split[f] = src[f];
+  }
   __shared__ int s_warp[32];
   __shared__ int s_carry;
   const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;

@@ -51,54 +51,60 @@ __device__ __forceinline__ double leaf_gain(double g, double h, const DevParams&
   return -(2.0 * sg * out + (h + P.lambda_l2) * out * out);
 }
 
-struct ScanBest {
+struct Cand {          // one threshold candidate
   double gain, left_g, left_h;
-  int t;           // scan position of the winner
-  int left_count;
+  int t, left_count;
 };
 
-// argmax over lanes; prefer_high: among equal gains keep the larger t (reverse scan) else the smaller t
-__device__ __forceinline__ ScanBest warp_best(ScanBest b, bool prefer_high) {
-  for (int o = 16; o > 0; o >>= 1) {
-    ScanBest x;
-    x.gain = __shfl_down_sync(FULL_MASK, b.gain, o);
-    x.left_g = __shfl_down_sync(FULL_MASK, b.left_g, o);
-    x.left_h = __shfl_down_sync(FULL_MASK, b.left_h, o);
-    x.t = __shfl_down_sync(FULL_MASK, b.t, o);
-    x.left_count = __shfl_down_sync(FULL_MASK, b.left_count, o);
-    const bool take = (x.gain > b.gain) ||
-                      (x.gain == b.gain && x.gain != LGB_MIN_SCORE && (prefer_high ? x.t > b.t : x.t < b.t));
-    if (take) b = x;
-  }
-  b.gain = __shfl_sync(FULL_MASK, b.gain, 0);
-  b.left_g = __shfl_sync(FULL_MASK, b.left_g, 0);
-  b.left_h = __shfl_sync(FULL_MASK, b.left_h, 0);
-  b.t = __shfl_sync(FULL_MASK, b.t, 0);
-  b.left_count = __shfl_sync(FULL_MASK, b.left_count, 0);
-  return b;
+__device__ __forceinline__ Cand cand_better(const Cand& a, const Cand& b, bool prefer_high) {
+  const bool take_b = (b.gain > a.gain) ||
+                      (b.gain == a.gain && b.gain != LGB_MIN_SCORE && (prefer_high ? b.t > a.t : b.t < a.t));
+  return take_b ? b : a;
 }
 
-// exclusive prefix (sum over lower lanes) of a 64-bit value
-__device__ __forceinline__ i64 warp_excl_prefix(i64 v, int lane) {
-  i64 inc = v;
-  for (int o = 1; o < 32; o <<= 1) {
-    const i64 x = __shfl_up_sync(FULL_MASK, inc, o);
-    if (lane >= o) inc += x;
+__device__ __forceinline__ Cand warp_best_cand(Cand c, bool prefer_high) {
+  for (int o = 16; o > 0; o >>= 1) {
+    Cand x;
+    x.gain = __shfl_xor_sync(FULL_MASK, c.gain, o);
+    x.left_g = __shfl_xor_sync(FULL_MASK, c.left_g, o);
+    x.left_h = __shfl_xor_sync(FULL_MASK, c.left_h, o);
+    x.t = __shfl_xor_sync(FULL_MASK, c.t, o);
+    x.left_count = __shfl_xor_sync(FULL_MASK, c.left_count, o);
+    c = cand_better(c, x, prefer_high);
   }
-  return inc - v;
+  return c;
 }
+
 __device__ __forceinline__ i64 warp_sum(i64 v) {
   for (int o = 16; o > 0; o >>= 1) v += __shfl_xor_sync(FULL_MASK, v, o);
   return v;
 }
 
-// One warp: FindBestThreshold for one numerical feature whose nt = num_bin - offset histogram entries
-// data_[t] sit in registers (gi/hi, 8 consecutive t per lane).  Writes *out (all lanes hold the same value).
-__device__ void scan_feature_warp(const i64 (&gi)[BINS_PER_LANE], const i64 (&hi)[BINS_PER_LANE], int nt,
-                                  const DevFeat& F, double sum_g, double leaf_sum_h, int num_data,
-                                  double parent_output, const DevParams& P, double inv_g, double inv_h,
-                                  DevSplit* out, int* splittable_out) {
-  const int lane = threadIdx.x & 31;
+#define FS_THREADS 256
+#define FS_WARPS (FS_THREADS / 32)
+
+// Shared-memory work area of one (feature, leaf) block.
+struct ScanSmem {
+  double gd[256], hd[256];      // data_[t] as doubles (after FixHistogram)
+  double sgd[256], shd[256];    // the smaller leaf's entries (larger-leaf blocks: needed to redo its FixHistogram)
+  double RG[256], RH[256];      // reverse scan: sum_right_gradient / sum_right_hessian after adding bin t
+  double LG[256], LH[256];      // forward scan: sum_left_* after adding bin t
+  int cnt[256], RC[256], LC[256];
+  double base_g, base_h; int base_c;   // forward scan start (implicit first bin of NA features with offset 1)
+  Cand wbest[2][FS_WARPS];
+  int wsplit[FS_WARPS];
+};
+
+// FindBestThreshold for one numerical feature, one block.  The floating-point accumulations of the reference
+// (FixHistogram's sequential subtraction and the two sequential scans that start from kEpsilon) are replayed in the
+// reference's order by four single threads on four different warps -- each chain is <= 256 dependent DADDs -- so that
+// whenever the histogram entries themselves are exact (always the case for the leaves where ties occur) every sum
+// that enters a gain is bit-identical to the reference's.  Gains (two fp64 divisions per threshold) are then
+// evaluated one threshold per thread and reduced with the reference's tie rules.
+__device__ void scan_feature_block(ScanSmem& S, int nt, const DevFeat& F, double sum_g, double leaf_sum_h,
+                                   int num_data, double parent_output, const DevParams& P, DevSplit* out,
+                                   int* splittable_out) {
+  const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
   const double sum_h = leaf_sum_h + (double)(2 * 1e-15f);  // FindBestThreshold: sum_hessian + 2 * kEpsilon
   const double cnt_factor = num_data / sum_h;
   const double min_gain_shift = leaf_gain(sum_g, sum_h, P, num_data, parent_output) + P.min_gain_to_split;
@@ -106,113 +112,89 @@ __device__ void scan_feature_warp(const i64 (&gi)[BINS_PER_LANE], const i64 (&hi
   const bool two_way = F.num_bin > 2 && F.missing_type != LGBCU_MISSING_NONE;
   const bool skip_default = two_way && F.missing_type == LGBCU_MISSING_ZERO;
   const bool na_missing = two_way && F.missing_type == LGBCU_MISSING_NAN;
+  const bool implicit_first = na_missing && offset == 1;
+  const int t_hi = nt - 1 - (na_missing ? 1 : 0), t_lo = 1 - offset;  // reverse range
+  const int t_end = nt - 2;                                            // forward range [0, t_end]
 
-  int cnt[BINS_PER_LANE];
-#pragma unroll
-  for (int k = 0; k < BINS_PER_LANE; ++k) {
-    const int t = lane * BINS_PER_LANE + k;
-    cnt[k] = (t < nt) ? round_int(((double)hi[k] * inv_h) * cnt_factor) : 0;
-  }
-  int splittable = 0;
-
-  // ---------------- REVERSE: t from nt-1-NA down to 1-offset, right side accumulates ----------------
-  ScanBest rb; rb.gain = LGB_MIN_SCORE; rb.t = -1000; rb.left_g = 0; rb.left_h = 0; rb.left_count = 0;
-  {
-    const int t_hi = nt - 1 - (na_missing ? 1 : 0), t_lo = 1 - offset;
-    i64 lg = 0, lh = 0, lc = 0;
-    bool inc[BINS_PER_LANE];
-#pragma unroll
-    for (int k = 0; k < BINS_PER_LANE; ++k) {
-      const int t = lane * BINS_PER_LANE + k;
-      inc[k] = t >= t_lo && t <= t_hi && !(skip_default && (t + offset) == F.default_bin);
-      if (inc[k]) { lg += gi[k]; lh += hi[k]; lc += cnt[k]; }
+  S.cnt[tid] = (tid < nt) ? round_int(S.hd[tid] * cnt_factor) : 0;
+  __syncthreads();
+  // ---- four sequential chains on four warps
+  if (tid == 0) {  // reverse sums
+    double ag = 0.0f, ah = LGB_EPS;
+    for (int t = t_hi; t >= t_lo; --t) {
+      if (skip_default && (t + offset) == F.default_bin) continue;
+      ag += S.gd[t]; ah += S.hd[t];
+      S.RG[t] = ag; S.RH[t] = ah;
     }
-    // sums over higher lanes = total - inclusive prefix
-    const i64 tg = warp_sum(lg), th = warp_sum(lh), tc = warp_sum(lc);
-    i64 ag = tg - (warp_excl_prefix(lg, lane) + lg);
-    i64 ah = th - (warp_excl_prefix(lh, lane) + lh);
-    i64 ac = tc - (warp_excl_prefix(lc, lane) + lc);
-#pragma unroll
-    for (int k = BINS_PER_LANE - 1; k >= 0; --k) {
-      if (!inc[k]) continue;
-      ag += gi[k]; ah += hi[k]; ac += cnt[k];
-      const double right_g = (double)ag * inv_g;
-      const double right_h = LGB_EPS + (double)ah * inv_h;
-      const int right_cnt = (int)ac;
-      if (right_cnt < P.min_data_in_leaf || right_h < P.min_sum_hessian) continue;
-      const int left_cnt = num_data - right_cnt;
-      if (left_cnt < P.min_data_in_leaf) continue;  // the reference breaks: monotone, same set
-      const double left_h = sum_h - right_h;
-      if (left_h < P.min_sum_hessian) continue;
-      const double left_g = sum_g - right_g;
-      const double gain = leaf_gain(left_g, left_h, P, left_cnt, parent_output) +
-                          leaf_gain(right_g, right_h, P, right_cnt, parent_output);
-      if (gain <= min_gain_shift) continue;
-      splittable = 1;
-      if (gain > rb.gain) {
-        rb.gain = gain; rb.left_g = left_g; rb.left_h = left_h; rb.left_count = left_cnt;
-        rb.t = lane * BINS_PER_LANE + k;
-      }
+  } else if (tid == 32) {  // reverse counts
+    int ac = 0;
+    for (int t = t_hi; t >= t_lo; --t) {
+      if (skip_default && (t + offset) == F.default_bin) continue;
+      ac += S.cnt[t];
+      S.RC[t] = ac;
     }
-    rb = warp_best(rb, true);
-  }
-  splittable = __any_sync(FULL_MASK, splittable);
-
-  DevSplit o;
-  o.gain = LGB_MIN_SCORE; o.feature = -1; o.real_feature = -1; o.threshold = 0; o.default_left = 1;
-  o.left_count = 0; o.right_count = 0; o.left_output = 0; o.right_output = 0;
-  o.left_sum_g = 0; o.left_sum_h = 0; o.right_sum_g = 0; o.right_sum_h = 0;
-  double best_gain_sel = LGB_MIN_SCORE, sel_left_g = 0, sel_left_h = 0;
-  int sel_left_cnt = 0;
-  bool have = false;
-  if (splittable && rb.gain > o.gain + min_gain_shift) {
-    have = true;
-    o.threshold = rb.t - 1 + offset;
-    o.default_left = 1;
-    best_gain_sel = rb.gain; sel_left_g = rb.left_g; sel_left_h = rb.left_h; sel_left_cnt = rb.left_count;
-    o.gain = rb.gain - min_gain_shift;
-  }
-
-  // ---------------- FORWARD (only with a missing bin and > 2 bins): left side accumulates ----------------
-  if (two_way) {
-    ScanBest fb; fb.gain = LGB_MIN_SCORE; fb.t = 100000; fb.left_g = 0; fb.left_h = 0; fb.left_count = 0;
-    const int t_end = nt - 2;
-    double base_g = 0.0, base_h = LGB_EPS;
-    int base_c = 0;
-    const bool implicit_first = na_missing && offset == 1;
+  } else if (tid == 64 && two_way) {  // forward sums
+    double lg = 0.0f, lh = LGB_EPS;
     if (implicit_first) {
-      i64 sg_all = 0, sh_all = 0, sc_all = 0;
-#pragma unroll
-      for (int k = 0; k < BINS_PER_LANE; ++k) {
-        if (lane * BINS_PER_LANE + k < nt) { sg_all += gi[k]; sh_all += hi[k]; sc_all += cnt[k]; }
+      lg = sum_g; lh = sum_h - LGB_EPS;
+      for (int i = 0; i < nt; ++i) { lg -= S.gd[i]; lh -= S.hd[i]; }
+    }
+    S.base_g = lg; S.base_h = lh;
+    for (int t = 0; t <= t_end; ++t) {
+      if (skip_default && (t + offset) == F.default_bin) continue;
+      lg += S.gd[t]; lh += S.hd[t];
+      S.LG[t] = lg; S.LH[t] = lh;
+    }
+  } else if (tid == 96 && two_way) {  // forward counts
+    int lc = 0;
+    if (implicit_first) {
+      lc = num_data;
+      for (int i = 0; i < nt; ++i) lc -= S.cnt[i];
+    }
+    S.base_c = lc;
+    for (int t = 0; t <= t_end; ++t) {
+      if (skip_default && (t + offset) == F.default_bin) continue;
+      lc += S.cnt[t];
+      S.LC[t] = lc;
+    }
+  }
+  __syncthreads();
+  // ---- one threshold per thread
+  int splittable = 0;
+  Cand rb; rb.gain = LGB_MIN_SCORE; rb.t = -1000; rb.left_g = 0; rb.left_h = 0; rb.left_count = 0;
+  Cand fb; fb.gain = LGB_MIN_SCORE; fb.t = 100000; fb.left_g = 0; fb.left_h = 0; fb.left_count = 0;
+  {
+    const int t = tid;
+    if (t >= t_lo && t <= t_hi && !(skip_default && (t + offset) == F.default_bin)) {
+      const double right_g = S.RG[t], right_h = S.RH[t];
+      const int right_cnt = S.RC[t];
+      if (!(right_cnt < P.min_data_in_leaf || right_h < P.min_sum_hessian)) {
+        const int left_cnt = num_data - right_cnt;
+        const double left_h = sum_h - right_h;
+        if (!(left_cnt < P.min_data_in_leaf) && !(left_h < P.min_sum_hessian)) {  // the reference breaks here: monotone
+          const double left_g = sum_g - right_g;
+          const double gain = leaf_gain(left_g, left_h, P, left_cnt, parent_output) +
+                              leaf_gain(right_g, right_h, P, right_cnt, parent_output);
+          if (!(gain <= min_gain_shift)) {
+            splittable = 1;
+            rb.gain = gain; rb.left_g = left_g; rb.left_h = left_h; rb.left_count = left_cnt; rb.t = t;
+          }
+        }
       }
-      sg_all = warp_sum(sg_all); sh_all = warp_sum(sh_all); sc_all = warp_sum(sc_all);
-      base_g = sum_g - (double)sg_all * inv_g;
-      base_h = (sum_h - LGB_EPS) - (double)sh_all * inv_h;
-      base_c = num_data - (int)sc_all;
     }
-    i64 lg = 0, lh = 0, lc = 0;
-    bool inc[BINS_PER_LANE];
-#pragma unroll
-    for (int k = 0; k < BINS_PER_LANE; ++k) {
-      const int t = lane * BINS_PER_LANE + k;
-      inc[k] = t <= t_end && !(skip_default && (t + offset) == F.default_bin);
-      if (inc[k]) { lg += gi[k]; lh += hi[k]; lc += cnt[k]; }
-    }
-    i64 ag = warp_excl_prefix(lg, lane), ah = warp_excl_prefix(lh, lane), ac = warp_excl_prefix(lc, lane);
-    int fsplittable = 0;
-    // k = -1 is the implicit-first-bin candidate (t = -1), evaluated by lane 0 only
-#pragma unroll
-    for (int k = -1; k < BINS_PER_LANE; ++k) {
-      if (k < 0) {
-        if (!(implicit_first && lane == 0 && t_end >= -1)) continue;
+  }
+  if (two_way) {
+    // thread t evaluates forward threshold t; thread FS_THREADS-1 also covers the implicit t = -1 candidate
+    for (int pass = 0; pass < 2; ++pass) {
+      int t; double left_g, left_h; int left_cnt;
+      if (pass == 0) {
+        t = tid;
+        if (!(t <= t_end && !(skip_default && (t + offset) == F.default_bin))) continue;
+        left_g = S.LG[t]; left_h = S.LH[t]; left_cnt = S.LC[t];
       } else {
-        if (!inc[k]) continue;
-        ag += gi[k]; ah += hi[k]; ac += cnt[k];
+        if (!(implicit_first && tid == FS_THREADS - 1)) continue;
+        t = -1; left_g = S.base_g; left_h = S.base_h; left_cnt = S.base_c;
       }
-      const double left_g = base_g + (double)ag * inv_g;
-      const double left_h = base_h + (double)ah * inv_h;
-      const int left_cnt = base_c + (int)ac;
       if (left_cnt < P.min_data_in_leaf || left_h < P.min_sum_hessian) continue;
       const int right_cnt = num_data - left_cnt;
       if (right_cnt < P.min_data_in_leaf) continue;
@@ -222,21 +204,42 @@ __device__ void scan_feature_warp(const i64 (&gi)[BINS_PER_LANE], const i64 (&hi
       const double gain = leaf_gain(left_g, left_h, P, left_cnt, parent_output) +
                           leaf_gain(right_g, right_h, P, right_cnt, parent_output);
       if (gain <= min_gain_shift) continue;
-      fsplittable = 1;
-      if (gain > fb.gain) {
-        fb.gain = gain; fb.left_g = left_g; fb.left_h = left_h; fb.left_count = left_cnt;
-        fb.t = (k < 0) ? -1 : lane * BINS_PER_LANE + k;
-      }
+      splittable = 1;
+      Cand c; c.gain = gain; c.left_g = left_g; c.left_h = left_h; c.left_count = left_cnt; c.t = t;
+      fb = cand_better(fb, c, false);
     }
-    fb = warp_best(fb, false);
-    if (__any_sync(FULL_MASK, fsplittable)) splittable = 1;
-    if (splittable && fb.gain > o.gain + min_gain_shift) {
-      have = true;
-      o.threshold = fb.t + offset;
-      o.default_left = 0;
-      best_gain_sel = fb.gain; sel_left_g = fb.left_g; sel_left_h = fb.left_h; sel_left_cnt = fb.left_count;
-      o.gain = fb.gain - min_gain_shift;
-    }
+  }
+  rb = warp_best_cand(rb, true);
+  fb = warp_best_cand(fb, false);
+  splittable = __any_sync(FULL_MASK, splittable);
+  if (lane == 0) { S.wbest[0][warp] = rb; S.wbest[1][warp] = fb; S.wsplit[warp] = splittable; }
+  __syncthreads();
+  if (tid != 0) return;
+  int any_split = 0;
+  for (int w = 0; w < FS_WARPS; ++w) {
+    any_split |= S.wsplit[w];
+    if (w) { rb = cand_better(rb, S.wbest[0][w], true); fb = cand_better(fb, S.wbest[1][w], false); }
+  }
+  DevSplit o;
+  o.gain = LGB_MIN_SCORE; o.feature = -1; o.real_feature = -1; o.threshold = 0; o.default_left = 1;
+  o.left_count = 0; o.right_count = 0; o.left_output = 0; o.right_output = 0;
+  o.left_sum_g = 0; o.left_sum_h = 0; o.right_sum_g = 0; o.right_sum_h = 0;
+  double sel_left_g = 0, sel_left_h = 0;
+  int sel_left_cnt = 0;
+  bool have = false;
+  // the reference runs the reverse scan first, then the forward scan; is_splittable_ set by either stays set
+  const bool rev_split = rb.gain > LGB_MIN_SCORE;
+  if (rev_split && rb.gain > o.gain + min_gain_shift) {
+    have = true;
+    o.threshold = rb.t - 1 + offset; o.default_left = 1;
+    sel_left_g = rb.left_g; sel_left_h = rb.left_h; sel_left_cnt = rb.left_count;
+    o.gain = rb.gain - min_gain_shift;
+  }
+  if (two_way && any_split && fb.gain > o.gain + min_gain_shift) {
+    have = true;
+    o.threshold = fb.t + offset; o.default_left = 0;
+    sel_left_g = fb.left_g; sel_left_h = fb.left_h; sel_left_cnt = fb.left_count;
+    o.gain = fb.gain - min_gain_shift;
   }
   if (have) {
     o.left_output = leaf_output(sel_left_g, sel_left_h, P, sel_left_cnt, parent_output);
@@ -248,12 +251,11 @@ __device__ void scan_feature_warp(const i64 (&gi)[BINS_PER_LANE], const i64 (&hi
     o.right_sum_g = sum_g - sel_left_g;
     o.right_sum_h = sum_h - sel_left_h - LGB_EPS;
   }
-  (void)best_gain_sel;
-  // a 2-bin (or <=2 bin) feature whose mapper carries a NaN bin: FuncForNumricalL3's last branch
+  // a <=2-bin feature whose mapper carries a NaN bin: FuncForNumricalL3's last branch
   if (!two_way && F.missing_type == LGBCU_MISSING_NAN) o.default_left = 0;
   o.gain *= F.penalty;  // FindBestThreshold: output->gain *= meta_->penalty
   *out = o;
-  *splittable_out = splittable;
+  *splittable_out = any_split;
 }
 
 // ComputeBestSplitForFeature (serial_tree_learner.cpp:709-718): the reference tests `leaf_index() == 0`, which holds
@@ -275,80 +277,96 @@ __device__ __forceinline__ bool split_better(double ga, int fa, double gb, int f
 }
 
 // mode 0: training (smaller/larger from DevCtl, control step at the end);
-// mode 1: explicit single leaf, no control (step-wise API / tests)
-__global__ void __launch_bounds__(64) k_find_split(DevView V, int mode, int leaf_arg) {
+// mode 1: explicit single leaf, no control (step-wise API / tests).
+// grid = (num_features, 2): blockIdx.y = 0 scans the smaller leaf, 1 forms larger = parent - smaller and scans it.
+__global__ void __launch_bounds__(FS_THREADS) k_find_split(DevView V, int mode, int leaf_arg) {
+  __shared__ ScanSmem S;
   __shared__ int s_last;
   DevCtl* c = V.ctl;
   if (mode == 0 && c->done) return;
-  const int f = blockIdx.x;
-  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+  const int f = blockIdx.x, sel = blockIdx.y;
+  const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
   const bool active = (mode == 1) || !c->skip_find;
   const int smaller = (mode == 1) ? leaf_arg : c->smaller;
   const int larger = (mode == 1) ? -1 : c->larger;
+  const int my_leaf = sel == 0 ? smaller : larger;
 
-  if (active && f < V.num_features) {
+  if (active && my_leaf >= 0 && f < V.num_features) {
     const DevFeat F = V.feats[f];
     const DevLeaf Ls = V.leaves[smaller];
     int used = V.feat_used[f] != 0;
-    if (larger >= 0) used = used && V.splittable[(size_t)V.leaves[larger].slot * V.num_features + f] != 0;
+    // a feature with no valid threshold in the parent is skipped in both children (serial_tree_learner.cpp:319-326);
+    // k_part_scan snapshotted the parent's flags, so sibling blocks cannot race on them
+    if (larger >= 0) used = used && V.parent_split[f] != 0;
     const int nt = F.num_bin - F.offset;
     const double inv_g = c->inv_g, inv_h = c->inv_h;
-    HistEntry* hs = V.pool + (size_t)Ls.slot * V.total_bin + F.hist_base;  // slot 0 of the group
-    i64 gi[BINS_PER_LANE], hi[BINS_PER_LANE];
-    if (warp == 0) {
-      DevSplit o; int sp = 0;
-      if (!used) {
-        o.gain = LGB_MIN_SCORE; o.feature = -1; o.real_feature = -1;
-      } else {
-        // load data_[t] = slot 1+t ; FixHistogram: the most-frequent bin's entry is what stored-value 0 collected
-        const HistEntry e0 = hs[0];
-#pragma unroll
-        for (int k = 0; k < BINS_PER_LANE; ++k) {
-          const int t = lane * BINS_PER_LANE + k;
-          HistEntry e; e.g = 0; e.h = 0;
-          if (t < nt) {
-            if (F.mfb > 0 && t == F.mfb) { e = e0; hs[1 + t] = e0; }
-            else e = hs[1 + t];
+    HistEntry* hs = V.pool + (size_t)Ls.slot * V.total_bin + F.hist_base;  // smaller leaf, slot 0 of the group
+    double2* fix_s = V.mfb_fix + (size_t)Ls.slot * V.num_features + f;
+    DevSplit o; int sp = 0;
+    o.gain = LGB_MIN_SCORE; o.feature = -1; o.real_feature = -1;
+    if (sel == 0) {
+      if (used) {
+        HistEntry e; e.g = 0; e.h = 0;
+        if (tid < nt) e = hs[1 + tid];
+        S.gd[tid] = (double)e.g * inv_g; S.hd[tid] = (double)e.h * inv_h;
+        __syncthreads();
+        if (F.mfb > 0) {
+          // Dataset::FixHistogram (dataset.cpp:1410-1428), in the reference's order and precision
+          if (tid == 0) {
+            double vg = Ls.sum_g, vh = Ls.sum_h;
+            for (int i = 0; i < F.num_bin; ++i) if (i != F.mfb) vg -= S.gd[i];
+            for (int i = 0; i < F.num_bin; ++i) if (i != F.mfb) vh -= S.hd[i];
+            S.gd[F.mfb] = vg; S.hd[F.mfb] = vh;
+            *fix_s = make_double2(vg, vh);
+            hs[1 + F.mfb] = hs[0];  // exact integer twin, used by later subtractions / exports
           }
-          gi[k] = e.g; hi[k] = e.h;
+          __syncthreads();
         }
-        const double parent_output = parent_output_of(Ls, smaller, V.p);
-        scan_feature_warp(gi, hi, nt, F, Ls.sum_g, Ls.sum_h, Ls.gcount, parent_output, V.p, inv_g, inv_h, &o, &sp);
+        scan_feature_block(S, nt, F, Ls.sum_g, Ls.sum_h, Ls.gcount, parent_output_of(Ls, smaller, V.p), V.p, &o, &sp);
         o.feature = f; o.real_feature = F.real_index;
       }
-      if (lane == 0) {
+      if (tid == 0) {
         V.feat_best[f] = o;
         V.splittable[(size_t)Ls.slot * V.num_features + f] = (int8_t)sp;
       }
-    }
-    __syncthreads();
-    if (warp == 1 && larger >= 0) {
+    } else {
       const DevLeaf Ll = V.leaves[larger];
-      DevSplit o; int sp = 0;
-      if (!used) {
-        o.gain = LGB_MIN_SCORE; o.feature = -1; o.real_feature = -1;
-      } else {
+      if (used) {
         HistEntry* hl = V.pool + (size_t)Ll.slot * V.total_bin + F.hist_base;  // holds the parent
-#pragma unroll
-        for (int k = 0; k < BINS_PER_LANE; ++k) {
-          const int t = lane * BINS_PER_LANE + k;
-          HistEntry e; e.g = 0; e.h = 0;
-          if (t < nt) {
-            const HistEntry a = hl[1 + t], b = hs[1 + t];
-            e.g = a.g - b.g; e.h = a.h - b.h;
-            hl[1 + t] = e;
+        double2* fix_l = V.mfb_fix + (size_t)Ll.slot * V.num_features + f;
+        HistEntry e; e.g = 0; e.h = 0; HistEntry b; b.g = 0; b.h = 0;
+        if (tid < nt) {
+          const HistEntry a = hl[1 + tid];
+          b = hs[1 + tid];
+          e.g = a.g - b.g; e.h = a.h - b.h;  // FeatureHistogram::Subtract, exact
+          hl[1 + tid] = e;
+        }
+        if (tid == FS_THREADS - 1) {  // the group's slot 0 (rows in the most-frequent bin)
+          const HistEntry a0 = hl[0], b0 = hs[0];
+          HistEntry e0; e0.g = a0.g - b0.g; e0.h = a0.h - b0.h;
+          hl[0] = e0;
+        }
+        S.gd[tid] = (double)e.g * inv_g; S.hd[tid] = (double)e.h * inv_h;
+        S.sgd[tid] = (double)b.g * inv_g; S.shd[tid] = (double)b.h * inv_h;
+        __syncthreads();
+        if (F.mfb > 0) {
+          // larger.data[mfb] = parent.data[mfb] (fixed when the parent was scanned) - smaller.data[mfb] (fixed now);
+          // the smaller leaf's FixHistogram is redone here so that this block does not wait for its sibling block
+          if (tid == 0) {
+            double vg = Ls.sum_g, vh = Ls.sum_h;
+            for (int i = 0; i < F.num_bin; ++i) if (i != F.mfb) vg -= S.sgd[i];
+            for (int i = 0; i < F.num_bin; ++i) if (i != F.mfb) vh -= S.shd[i];
+            const double2 pf = *fix_l;
+            const double lg = pf.x - vg, lh = pf.y - vh;
+            S.gd[F.mfb] = lg; S.hd[F.mfb] = lh;
+            *fix_l = make_double2(lg, lh);
           }
-          gi[k] = e.g; hi[k] = e.h;
+          __syncthreads();
         }
-        if (lane == 0) {  // the group's slot 0 (rows in the most-frequent bin)
-          const HistEntry a = hl[0], b = hs[0];
-          HistEntry e; e.g = a.g - b.g; e.h = a.h - b.h;
-          hl[0] = e;
-        }
-        scan_feature_warp(gi, hi, nt, F, Ll.sum_g, Ll.sum_h, Ll.gcount, parent_output_of(Ll, larger, V.p), V.p, inv_g, inv_h, &o, &sp);
+        scan_feature_block(S, nt, F, Ll.sum_g, Ll.sum_h, Ll.gcount, parent_output_of(Ll, larger, V.p), V.p, &o, &sp);
         o.feature = f; o.real_feature = F.real_index;
       }
-      if (lane == 0) {
+      if (tid == 0) {
         V.feat_best[V.num_features + f] = o;
         if (used) V.splittable[(size_t)Ll.slot * V.num_features + f] = (int8_t)sp;
       }
@@ -360,7 +378,7 @@ __global__ void __launch_bounds__(64) k_find_split(DevView V, int mode, int leaf
   __syncthreads();
   if (threadIdx.x == 0) {
     const unsigned ticket = atomicAdd(&c->feat_done, 1u);
-    s_last = (ticket == gridDim.x - 1);
+    s_last = (ticket == gridDim.x * gridDim.y - 1);
   }
   __syncthreads();
   if (!s_last) return;
