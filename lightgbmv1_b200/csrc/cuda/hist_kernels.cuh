@@ -98,9 +98,9 @@ __global__ void __launch_bounds__(256) k_hist_global(DevView V, int leaf_arg, in
 }
 
 // rows each (tile, part) work item should at least have before another warp is recruited for the tile
-#define HIST_MIN_ROWS_PER_WARP 1024
+#define HIST_MIN_ROWS_PER_WARP 128
 
-__global__ void __launch_bounds__(HIST_WARPS_PER_BLOCK * 32, 1) k_hist_warp_private(DevView V, int leaf_arg, int regime) {
+__global__ void __launch_bounds__(HIST_WARPS_PER_BLOCK * 32, 1) k_hist_warp_private(DevView V, int leaf_arg, int regime, int min_rows) {
   extern __shared__ __align__(16) unsigned char smem[];
   int leaf;
   if (!hist_target(V, leaf_arg, &leaf)) return;
@@ -122,7 +122,7 @@ __global__ void __launch_bounds__(HIST_WARPS_PER_BLOCK * 32, 1) k_hist_warp_priv
   const int NW = gridDim.x * HIST_WARPS_PER_BLOCK;
   const int gw = blockIdx.x * HIST_WARPS_PER_BLOCK + warp;
   const int NT = V.num_tiles16;
-  int P = (L.count + HIST_MIN_ROWS_PER_WARP - 1) / HIST_MIN_ROWS_PER_WARP;
+  int P = (L.count + min_rows - 1) / min_rows;
   int cap = NW / NT; if (cap < 1) cap = 1;
   if (P > cap) P = cap;
   if (P < 1) P = 1;
@@ -176,13 +176,25 @@ __global__ void __launch_bounds__(HIST_WARPS_PER_BLOCK * 32, 1) k_hist_warp_priv
       __syncwarp();
       int n = r1 - base; if (n > 32) n = 32;
       if (n == 32) {
+        // 4 rows in flight: their 4 read-modify-writes are independent unless two rows of this lane's feature share
+        // a bin.  Duplicates are folded forward (the last row of a bin carries the sum, earlier ones add 0), all 4
+        // loads are issued before the 4 stores, and stores stay in row order, so the result is the sequential one.
 #pragma unroll
-        for (int j0 = 0; j0 < 32; j0 += 8) {
-          unsigned b[8]; i64 v[8];
-#pragma unroll
-          for (int j = 0; j < 8; ++j) { b[j] = sb8[(j0 + j) * 16 + fl]; v[j] = sv64[(j0 + j) * 2 + ch]; }
-#pragma unroll
-          for (int j = 0; j < 8; ++j) { i64* p = H + (b[j] * 32 + lane); *p += v[j]; }
+        for (int j0 = 0; j0 < 32; j0 += 4) {
+          const unsigned b0 = sb8[(j0 + 0) * 16 + fl], b1 = sb8[(j0 + 1) * 16 + fl];
+          const unsigned b2 = sb8[(j0 + 2) * 16 + fl], b3 = sb8[(j0 + 3) * 16 + fl];
+          i64 v0 = sv64[(j0 + 0) * 2 + ch], v1 = sv64[(j0 + 1) * 2 + ch];
+          i64 v2 = sv64[(j0 + 2) * 2 + ch], v3 = sv64[(j0 + 3) * 2 + ch];
+          if (b1 == b0) { v1 += v0; v0 = 0; }
+          if (b2 == b0) { v2 += v0; v0 = 0; }
+          if (b2 == b1) { v2 += v1; v1 = 0; }
+          if (b3 == b0) { v3 += v0; v0 = 0; }
+          if (b3 == b1) { v3 += v1; v1 = 0; }
+          if (b3 == b2) { v3 += v2; v2 = 0; }
+          i64* p0 = H + (b0 * 32 + lane); i64* p1 = H + (b1 * 32 + lane);
+          i64* p2 = H + (b2 * 32 + lane); i64* p3 = H + (b3 * 32 + lane);
+          const i64 a0 = *p0, a1 = *p1, a2 = *p2, a3 = *p3;
+          *p0 = a0 + v0; *p1 = a1 + v1; *p2 = a2 + v2; *p3 = a3 + v3;
         }
       } else {
         for (int j = 0; j < n; ++j) {

@@ -5,6 +5,7 @@
 #include <cstddef>
 #include <cstdarg>
 #include <cstdio>
+#include <cstdlib>
 #include <cstring>
 #include <string>
 #include <vector>
@@ -112,6 +113,7 @@ struct LgbCuContext {
   DevSplit* h_split = nullptr;
   // config
   int hist_mode = LGBCU_HIST_AUTO;
+  int hist_min_rows = HIST_MIN_ROWS_PER_WARP;
   int objective = LGBCU_OBJ_NONE; double obj_p[3] = {0, 0, 0};
   int root_count = 0; bool tree_begun = false;
   // profiling
@@ -174,7 +176,7 @@ int launch_hist(LgbCuContext* c, int leaf_arg) {
   }
   if (mode == LGBCU_HIST_WARP_PRIVATE || mode == LGBCU_HIST_AUTO) {
     const int regime = mode == LGBCU_HIST_AUTO ? 2 : 0;
-    LAUNCH(k_hist_warp_private, c->num_sms, HIST_WARPS_PER_BLOCK * 32, HIST_SMEM_BYTES, c->stream, V, leaf_arg, regime);
+    LAUNCH(k_hist_warp_private, c->num_sms, HIST_WARPS_PER_BLOCK * 32, HIST_SMEM_BYTES, c->stream, V, leaf_arg, regime, c->hist_min_rows);
   }
   CU(cudaGetLastError());
   return 0;
@@ -237,6 +239,7 @@ int lgbcu_create(int device_id, LgbCuContext** out) {
   cudaDeviceProp prop;
   CU(cudaGetDeviceProperties(&prop, device_id));
   c->num_sms = prop.multiProcessorCount;
+  if (const char* e = std::getenv("LGBCU_HIST_MIN_ROWS")) { const int v = std::atoi(e); if (v >= 32) c->hist_min_rows = v; }
   CU(cudaStreamCreateWithFlags(&c->stream, cudaStreamNonBlocking));
   CU(dev_alloc(&c->d_ctl, 1));
   CU(cudaMemset(c->d_ctl, 0, sizeof(DevCtl)));

@@ -80,6 +80,53 @@ __device__ __forceinline__ i64 warp_sum(i64 v) {
   return v;
 }
 
+// One thread walks a shared-memory array in index order accumulating two independent fp64 chains (gradient,
+// hessian) exactly as a sequential CPU loop would; operands are fetched 8 at a time so that only the DADD latency
+// is on the critical path.  `sign` = +1 adds, -1 subtracts (x - v is computed as x + (-v): identical in IEEE).
+// Entries equal to `skip_t` contribute +0.0, which leaves a running sum bit-unchanged.
+template <int DIR>
+__device__ __forceinline__ void chain2(const double* __restrict__ g, const double* __restrict__ h, double* og, double* oh,
+                                       int t_first, int t_last, int skip_t, double sign, double* ag_io, double* ah_io) {
+  double ag = *ag_io, ah = *ah_io;
+  const int count = DIR > 0 ? t_last - t_first + 1 : t_first - t_last + 1;
+  for (int base = 0; base < count; base += 8) {
+    double vg[8], vh[8];
+#pragma unroll
+    for (int k = 0; k < 8; ++k) {
+      const int t = t_first + DIR * (base + k);
+      const bool ok = (base + k) < count && t != skip_t;
+      vg[k] = ok ? sign * g[t] : 0.0;
+      vh[k] = ok ? sign * h[t] : 0.0;
+    }
+#pragma unroll
+    for (int k = 0; k < 8; ++k) {
+      ag += vg[k]; ah += vh[k];
+      if (og && (base + k) < count) { const int t = t_first + DIR * (base + k); og[t] = ag; oh[t] = ah; }
+    }
+  }
+  *ag_io = ag; *ah_io = ah;
+}
+template <int DIR>
+__device__ __forceinline__ void chain_cnt(const int* __restrict__ c, int* out, int t_first, int t_last, int skip_t,
+                                          int sign, int* acc_io) {
+  int acc = *acc_io;
+  const int count = DIR > 0 ? t_last - t_first + 1 : t_first - t_last + 1;
+  for (int base = 0; base < count; base += 8) {
+    int v[8];
+#pragma unroll
+    for (int k = 0; k < 8; ++k) {
+      const int t = t_first + DIR * (base + k);
+      v[k] = ((base + k) < count && t != skip_t) ? sign * c[t] : 0;
+    }
+#pragma unroll
+    for (int k = 0; k < 8; ++k) {
+      acc += v[k];
+      if (out && (base + k) < count) out[t_first + DIR * (base + k)] = acc;
+    }
+  }
+  *acc_io = acc;
+}
+
 #define FS_THREADS 256
 #define FS_WARPS (FS_THREADS / 32)
 
@@ -119,44 +166,29 @@ __device__ void scan_feature_block(ScanSmem& S, int nt, const DevFeat& F, double
   S.cnt[tid] = (tid < nt) ? round_int(S.hd[tid] * cnt_factor) : 0;
   __syncthreads();
   // ---- four sequential chains on four warps
+  const int skip_t = skip_default ? (int)F.default_bin - offset : -1000;  // data_ index of the skipped default bin
   if (tid == 0) {  // reverse sums
     double ag = 0.0f, ah = LGB_EPS;
-    for (int t = t_hi; t >= t_lo; --t) {
-      if (skip_default && (t + offset) == F.default_bin) continue;
-      ag += S.gd[t]; ah += S.hd[t];
-      S.RG[t] = ag; S.RH[t] = ah;
-    }
+    chain2<-1>(S.gd, S.hd, S.RG, S.RH, t_hi, t_lo, skip_t, 1.0, &ag, &ah);
   } else if (tid == 32) {  // reverse counts
     int ac = 0;
-    for (int t = t_hi; t >= t_lo; --t) {
-      if (skip_default && (t + offset) == F.default_bin) continue;
-      ac += S.cnt[t];
-      S.RC[t] = ac;
-    }
+    chain_cnt<-1>(S.cnt, S.RC, t_hi, t_lo, skip_t, 1, &ac);
   } else if (tid == 64 && two_way) {  // forward sums
     double lg = 0.0f, lh = LGB_EPS;
     if (implicit_first) {
       lg = sum_g; lh = sum_h - LGB_EPS;
-      for (int i = 0; i < nt; ++i) { lg -= S.gd[i]; lh -= S.hd[i]; }
+      chain2<1>(S.gd, S.hd, nullptr, nullptr, 0, nt - 1, -1000, -1.0, &lg, &lh);
     }
     S.base_g = lg; S.base_h = lh;
-    for (int t = 0; t <= t_end; ++t) {
-      if (skip_default && (t + offset) == F.default_bin) continue;
-      lg += S.gd[t]; lh += S.hd[t];
-      S.LG[t] = lg; S.LH[t] = lh;
-    }
+    chain2<1>(S.gd, S.hd, S.LG, S.LH, 0, t_end, skip_t, 1.0, &lg, &lh);
   } else if (tid == 96 && two_way) {  // forward counts
     int lc = 0;
     if (implicit_first) {
       lc = num_data;
-      for (int i = 0; i < nt; ++i) lc -= S.cnt[i];
+      chain_cnt<1>(S.cnt, nullptr, 0, nt - 1, -1000, -1, &lc);
     }
     S.base_c = lc;
-    for (int t = 0; t <= t_end; ++t) {
-      if (skip_default && (t + offset) == F.default_bin) continue;
-      lc += S.cnt[t];
-      S.LC[t] = lc;
-    }
+    chain_cnt<1>(S.cnt, S.LC, 0, t_end, skip_t, 1, &lc);
   }
   __syncthreads();
   // ---- one threshold per thread
@@ -314,8 +346,7 @@ __global__ void __launch_bounds__(FS_THREADS) k_find_split(DevView V, int mode, 
           // Dataset::FixHistogram (dataset.cpp:1410-1428), in the reference's order and precision
           if (tid == 0) {
             double vg = Ls.sum_g, vh = Ls.sum_h;
-            for (int i = 0; i < F.num_bin; ++i) if (i != F.mfb) vg -= S.gd[i];
-            for (int i = 0; i < F.num_bin; ++i) if (i != F.mfb) vh -= S.hd[i];
+            chain2<1>(S.gd, S.hd, nullptr, nullptr, 0, F.num_bin - 1, F.mfb, -1.0, &vg, &vh);
             S.gd[F.mfb] = vg; S.hd[F.mfb] = vh;
             *fix_s = make_double2(vg, vh);
             hs[1 + F.mfb] = hs[0];  // exact integer twin, used by later subtractions / exports
@@ -354,8 +385,7 @@ __global__ void __launch_bounds__(FS_THREADS) k_find_split(DevView V, int mode, 
           // the smaller leaf's FixHistogram is redone here so that this block does not wait for its sibling block
           if (tid == 0) {
             double vg = Ls.sum_g, vh = Ls.sum_h;
-            for (int i = 0; i < F.num_bin; ++i) if (i != F.mfb) vg -= S.sgd[i];
-            for (int i = 0; i < F.num_bin; ++i) if (i != F.mfb) vh -= S.shd[i];
+            chain2<1>(S.sgd, S.shd, nullptr, nullptr, 0, F.num_bin - 1, F.mfb, -1.0, &vg, &vh);
             const double2 pf = *fix_l;
             const double lg = pf.x - vg, lh = pf.y - vh;
             S.gd[F.mfb] = lg; S.hd[F.mfb] = lh;
