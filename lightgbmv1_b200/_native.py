@@ -73,7 +73,7 @@ LGBCU_SYMBOLS = [
     "lgbcu_begin_tree", "lgbcu_hist_build", "lgbcu_hist_read", "lgbcu_num_total_bin", "lgbcu_hist_subtract",
     "lgbcu_find_best_split", "lgbcu_partition", "lgbcu_leaf_indices", "lgbcu_set_leaf_sums",
     "lgbcu_get_leaf_sums", "lgbcu_train_tree", "lgbcu_comm_unique_id", "lgbcu_comm_init", "lgbcu_comm_destroy", "lgbcu_comm_allreduce_sum_f64",
-    "lgbcu_profile_enable", "lgbcu_profile_read", "lgbcu_partition_rows_noalloc",
+    "lgbcu_profile_enable", "lgbcu_profile_read", "lgbcu_partition_rows_noalloc", "lgbcu_profile_phases",
 ]
 
 lib.lgbcu_last_error.restype = C.c_char_p
@@ -313,6 +313,11 @@ class CudaLearner:
 
     def profile_enable(self, on: bool) -> None:
         check(lib.lgbcu_profile_enable(self._h, C.c_int(1 if on else 0)))
+
+    def profile_phases(self):
+        a = (C.c_double * 8)()
+        check(lib.lgbcu_profile_phases(self._h, a))
+        return list(a)
 
     def profile_read(self, reset=False):
         ms, calls, nbytes = C.c_double(), C.c_int64(), C.c_double()

@@ -68,7 +68,8 @@ struct DevCtl {
   unsigned pad0;
   long long global_root;  // root rows over all ranks   } adjacent: one 2 x int64 sum all-reduce
   long long global_rows;  // dataset rows over all ranks }
-  unsigned long long prof_hist_rows, prof_hist_rows_indexed, prof_hist_calls;
+  unsigned long long prof_hist_rows, prof_hist_rows_indexed, prof_hist_calls, prof_hist_ns;
+  unsigned long long prof_phase_ns[8];  // persistent kernel: hist, root, find, control, flags, scan, scatter, (spare)
 };
 
 struct DevParams {   // LgbCuTreeParams + derived switches

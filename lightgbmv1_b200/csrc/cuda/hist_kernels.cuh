@@ -6,21 +6,28 @@
 // exact and order independent, so the result is bit-reproducible for any grid shape, any number of GPUs and
 // any atomic ordering; the only rounding is the per-row quantisation (<= 2^-38 of max|g| for 10^7 rows).
 //
-// Two kernels:
-//   k_hist_global       : one thread per (row, 16-feature chunk), REDG.ADD.64 straight into the pool slot.
-//                         Launch-latency friendly, used for small leaves.
-//   k_hist_warp_private : each warp owns a private 64 KB shared-memory sub-histogram for one tile of 16
-//                         features x {g,h}; lane l = (channel, feature) so the 32 lanes of a warp always
-//                         hit 32 different columns -> plain LDS/IADD/STS, no atomics, no bank conflicts
-//                         (row stride 256 B keeps lane l on bank pair l).  Flushed with REDG.ADD.64.
+// Two code paths, chosen ON DEVICE from the leaf size (no host round trip):
+//   global atomics : one thread per (row, 16-feature chunk), REDG.ADD.64 straight into the pool slot.  Small
+//                    leaves (< HIST_SMALL_LEAF_ROWS rows), where zeroing / flushing a 64 KB sub-histogram per
+//                    warp would cost more than the rows themselves.
+//   warp private   : warps 0..2 of a block each own a private 64 KB shared-memory sub-histogram for one tile
+//                    of 16 features x {g,h}; lane l = (channel, feature) so the 32 lanes of a warp always hit
+//                    32 different columns -> plain LDS / IADD / STS, no atomics, and with the layout
+//                    [bin][channel][16 features] (256 B per bin) lane l always sits on bank pair l: no bank
+//                    conflicts for any bin pattern.  Four rows are kept in flight per warp (duplicate bins are
+//                    folded forward).  The three sub-histograms of a block are summed in shared memory and
+//                    flushed once with REDG.ADD.64.
 #pragma once
 #include "dev_types.cuh"
 
-#define HIST_WARPS_PER_BLOCK 3
-#define HIST_ROWS_SMEM 256                      /* bin rows per private sub-histogram */
-#define HIST_SUB_BYTES (HIST_ROWS_SMEM * 32 * 8) /* 64 KB */
-#define HIST_STAGE_BYTES 1024                    /* per warp: 32 x 16 B bins + 32 x 16 B (gq,hq) */
+#define HIST_THREADS 256                          /* block size of every kernel that contains a histogram phase */
+#define HIST_WARPS_PER_BLOCK 3                    /* warps that accumulate (the private sub-histograms fill smem) */
+#define HIST_ROWS_SMEM 256                        /* bin rows per private sub-histogram */
+#define HIST_SUB_BYTES (HIST_ROWS_SMEM * 32 * 8)  /* 64 KB */
+#define HIST_STAGE_BYTES 1024                     /* per warp: 32 x 16 B bins + 32 x 16 B (gq,hq) */
 #define HIST_SMEM_BYTES (HIST_WARPS_PER_BLOCK * (HIST_SUB_BYTES + HIST_STAGE_BYTES))
+#define HIST_SMALL_LEAF_ROWS 4096
+#define HIST_MIN_ROWS_PER_WARP 128                /* rows a warp should at least get before another block is recruited */
 
 __device__ __forceinline__ i64 to_fixed(float v, double scale) {
   return __double2ll_rn((double)v * scale);
@@ -39,37 +46,19 @@ __device__ __forceinline__ bool hist_target(const DevView& V, int leaf_arg, int*
   return *leaf >= 0;
 }
 
-// AUTO mode: both kernels are enqueued every split with a `regime`; each looks at the leaf size on device and
-// only the one whose regime it is does the work (the other exits after reading a few words), so no host
-// round trip is needed to choose.  regime 0 = always run, 1 = only small leaves, 2 = only large leaves.
-#define HIST_SMALL_LEAF_ROWS 4096
-__device__ __forceinline__ bool hist_regime_ok(int regime, int count) {
-  if (regime == 1) return count < HIST_SMALL_LEAF_ROWS;
-  if (regime == 2) return count >= HIST_SMALL_LEAF_ROWS;
-  return true;
-}
-
-__global__ void __launch_bounds__(256) k_hist_global(DevView V, int leaf_arg, int regime) {
-  int leaf;
-  if (!hist_target(V, leaf_arg, &leaf)) return;
-  const DevLeaf L = V.leaves[leaf];
-  if (!hist_regime_ok(regime, L.count)) return;
+__device__ void hist_global_path(const DevView& V, const DevLeaf& L, bool identity, int bid, int nblocks) {
   const DevCtl* c = V.ctl;
-  const bool identity = c->root_identity && leaf == 0 && L.count == V.num_data;
   const double sg = c->scale_g, sh = c->scale_h;
   const int* idx = V.indices[L.buf] + L.begin;
   HistEntry* out = V.pool + (size_t)L.slot * V.total_bin;
   const int nchunk = V.num_tiles16;
   const long long total = (long long)L.count * nchunk;
-  i64 tg = 0, th = 0;
-  for (long long p = blockIdx.x * (long long)blockDim.x + threadIdx.x; p < total;
-       p += (long long)gridDim.x * blockDim.x) {
+  for (long long p = bid * (long long)blockDim.x + threadIdx.x; p < total; p += (long long)nblocks * blockDim.x) {
     const int pos = (int)(p / nchunk);
     const int ck = (int)(p - (long long)pos * nchunk);
     const int row = identity ? pos : idx[pos];
     const uint4 q = *reinterpret_cast<const uint4*>(V.bins + (size_t)row * V.row_stride + ck * 16);
     const i64 gq = to_fixed(V.grad[row], sg), hq = to_fixed(V.hess[row], sh);
-    if (ck == 0) { tg += gq; th += hq; }
     const unsigned w[4] = {q.x, q.y, q.z, q.w};
 #pragma unroll
     for (int k = 0; k < 16; ++k) {
@@ -82,152 +71,147 @@ __global__ void __launch_bounds__(256) k_hist_global(DevView V, int leaf_arg, in
       }
     }
   }
-  // leaf totals (LeafSplits::Init for the root, src/treelearner/leaf_splits.hpp:66-79)
-  for (int o = 16; o > 0; o >>= 1) {
-    tg += __shfl_down_sync(0xffffffffu, tg, o);
-    th += __shfl_down_sync(0xffffffffu, th, o);
-  }
-  if ((threadIdx.x & 31) == 0 && (tg | th)) {
-    atomic_add_i64(&V.leaves[leaf].tot_g, tg);
-    atomic_add_i64(&V.leaves[leaf].tot_h, th);
-  }
-  if (blockIdx.x == 0 && threadIdx.x == 0) {
-    atomicAdd(&V.ctl->prof_hist_calls, 1ull);
-    atomicAdd(identity ? &V.ctl->prof_hist_rows : &V.ctl->prof_hist_rows_indexed, (unsigned long long)L.count);
-  }
 }
 
-// rows each (tile, part) work item should at least have before another warp is recruited for the tile
-#define HIST_MIN_ROWS_PER_WARP 128
-
-__global__ void __launch_bounds__(HIST_WARPS_PER_BLOCK * 32, 1) k_hist_warp_private(DevView V, int leaf_arg, int regime, int min_rows) {
-  extern __shared__ __align__(16) unsigned char smem[];
-  int leaf;
-  if (!hist_target(V, leaf_arg, &leaf)) return;
-  const DevLeaf L = V.leaves[leaf];
-  if (!hist_regime_ok(regime, L.count)) return;
+// smem: HIST_SMEM_BYTES of dynamic shared memory.  Called by all HIST_THREADS threads of every block.
+__device__ void hist_private_path(const DevView& V, const DevLeaf& L, bool identity, int bid, int nblocks, int min_rows,
+                                  unsigned char* smem) {
   const DevCtl* c = V.ctl;
-  const bool identity = c->root_identity && leaf == 0 && L.count == V.num_data;
   const double sg = c->scale_g, sh = c->scale_h;
-  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+  const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
   const int fl = lane & 15, ch = lane >> 4;
-
-  i64* H = reinterpret_cast<i64*>(smem + (size_t)warp * HIST_SUB_BYTES);
-  unsigned char* stage = smem + (size_t)HIST_WARPS_PER_BLOCK * HIST_SUB_BYTES + warp * HIST_STAGE_BYTES;
-  uint4* sbins = reinterpret_cast<uint4*>(stage);              // [32] one 16-byte chunk per staged row
+  const bool worker = warp < HIST_WARPS_PER_BLOCK;
+  const int wslot = worker ? warp : 0;
+  i64* H = reinterpret_cast<i64*>(smem + (size_t)wslot * HIST_SUB_BYTES);
+  const i64* H0 = reinterpret_cast<const i64*>(smem);
+  const i64* H1 = reinterpret_cast<const i64*>(smem + (size_t)HIST_SUB_BYTES);
+  const i64* H2 = reinterpret_cast<const i64*>(smem + (size_t)2 * HIST_SUB_BYTES);
+  unsigned char* stage = smem + (size_t)HIST_WARPS_PER_BLOCK * HIST_SUB_BYTES + wslot * HIST_STAGE_BYTES;
+  uint4* sbins = reinterpret_cast<uint4*>(stage);                // [32] one 16-byte chunk per staged row
   longlong2* svals = reinterpret_cast<longlong2*>(stage + 512);  // [32] (gq, hq) per staged row
   const unsigned char* sb8 = stage;
   const i64* sv64 = reinterpret_cast<const i64*>(stage + 512);
 
-  const int NW = gridDim.x * HIST_WARPS_PER_BLOCK;
-  const int gw = blockIdx.x * HIST_WARPS_PER_BLOCK + warp;
   const int NT = V.num_tiles16;
-  int P = (L.count + min_rows - 1) / min_rows;
-  int cap = NW / NT; if (cap < 1) cap = 1;
-  if (P > cap) P = cap;
-  if (P < 1) P = 1;
-  int per = (L.count + P - 1) / P;
-  per = (per + 31) & ~31;
+  // block-level work items: (tile, part); a block's rows are split three ways over its accumulating warps
+  int PB = (L.count + HIST_WARPS_PER_BLOCK * min_rows - 1) / (HIST_WARPS_PER_BLOCK * min_rows);
+  int cap = nblocks / NT; if (cap < 1) cap = 1;
+  if (PB > cap) PB = cap;
+  if (PB < 1) PB = 1;
+  int per_block = (L.count + PB - 1) / PB;
+  per_block = (per_block + 95) / 96 * 96;  // three multiples of 32
+  const int per_warp = per_block / 3;
 
   const int* idx = V.indices[L.buf] + L.begin;
   HistEntry* out = V.pool + (size_t)L.slot * V.total_bin;
-  i64 tg = 0, th = 0;
 
-  for (int item = gw; item < NT * P; item += NW) {
-    const int tile = item / P, part = item - tile * P;
-    const int r0 = part * per;
-    int r1 = r0 + per; if (r1 > L.count) r1 = L.count;
-    if (r0 >= r1) continue;
-    // zero the private sub-histogram
-    {
+  for (int item = bid; item < NT * PB; item += nblocks) {
+    const int tile = item / PB, part = item - tile * PB;
+    const int b0 = part * per_block;
+    int b1 = b0 + per_block; if (b1 > L.count) b1 = L.count;
+    if (worker) {
+      // zero the private sub-histogram
       uint4* z = reinterpret_cast<uint4*>(H);
       const uint4 zero = make_uint4(0, 0, 0, 0);
 #pragma unroll 4
       for (int i = lane; i < HIST_SUB_BYTES / 16; i += 32) z[i] = zero;
-    }
-    __syncwarp();
-    const uint8_t* colbase = V.bins + tile * 16;
-    // software pipeline: the (index ->) row loads of batch k+1 are in flight while batch k is accumulated
-    uint4 nq = make_uint4(0, 0, 0, 0);
-    float ng = 0.f, nh = 0.f;
-    {
-      const int pos = r0 + lane;
-      if (pos < r1) {
-        const int row = identity ? pos : idx[pos];
-        nq = *reinterpret_cast<const uint4*>(colbase + (size_t)row * V.row_stride);
-        ng = V.grad[row]; nh = V.hess[row];
-      }
-    }
-    for (int base = r0; base < r1; base += 32) {
-      const uint4 q = nq;
-      const i64 gq = to_fixed(ng, sg), hq = to_fixed(nh, sh);
-      if (tile == 0) { tg += gq; th += hq; }
-      nq = make_uint4(0, 0, 0, 0); ng = 0.f; nh = 0.f;
-      {
-        const int pos = base + 32 + lane;
+      __syncwarp();
+      const int r0 = b0 + warp * per_warp;
+      int r1 = r0 + per_warp; if (r1 > b1) r1 = b1;
+      const uint8_t* colbase = V.bins + tile * 16;
+      // software pipeline: the (index ->) row loads of batch k+1 are in flight while batch k is accumulated
+      uint4 nq = make_uint4(0, 0, 0, 0);
+      float ng = 0.f, nh = 0.f;
+      if (r0 < r1) {
+        const int pos = r0 + lane;
         if (pos < r1) {
           const int row = identity ? pos : idx[pos];
           nq = *reinterpret_cast<const uint4*>(colbase + (size_t)row * V.row_stride);
           ng = V.grad[row]; nh = V.hess[row];
         }
       }
-      sbins[lane] = q;
-      svals[lane] = make_longlong2(gq, hq);
-      __syncwarp();
-      int n = r1 - base; if (n > 32) n = 32;
-      if (n == 32) {
-        // 4 rows in flight: their 4 read-modify-writes are independent unless two rows of this lane's feature share
-        // a bin.  Duplicates are folded forward (the last row of a bin carries the sum, earlier ones add 0), all 4
-        // loads are issued before the 4 stores, and stores stay in row order, so the result is the sequential one.
+      for (int base = r0; base < r1; base += 32) {
+        const uint4 q = nq;
+        const i64 gq = to_fixed(ng, sg), hq = to_fixed(nh, sh);
+        nq = make_uint4(0, 0, 0, 0); ng = 0.f; nh = 0.f;
+        {
+          const int pos = base + 32 + lane;
+          if (pos < r1) {
+            const int row = identity ? pos : idx[pos];
+            nq = *reinterpret_cast<const uint4*>(colbase + (size_t)row * V.row_stride);
+            ng = V.grad[row]; nh = V.hess[row];
+          }
+        }
+        sbins[lane] = q;
+        svals[lane] = make_longlong2(gq, hq);
+        __syncwarp();
+        int n = r1 - base; if (n > 32) n = 32;
+        if (n == 32) {
+          // 4 rows in flight: their 4 read-modify-writes are independent unless two rows of this lane's feature
+          // share a bin.  Duplicates are folded forward (the last row of a bin carries the sum, earlier ones add
+          // 0), all 4 loads are issued before the 4 stores, and stores stay in row order: the sequential result.
 #pragma unroll
-        for (int j0 = 0; j0 < 32; j0 += 4) {
-          const unsigned b0 = sb8[(j0 + 0) * 16 + fl], b1 = sb8[(j0 + 1) * 16 + fl];
-          const unsigned b2 = sb8[(j0 + 2) * 16 + fl], b3 = sb8[(j0 + 3) * 16 + fl];
-          i64 v0 = sv64[(j0 + 0) * 2 + ch], v1 = sv64[(j0 + 1) * 2 + ch];
-          i64 v2 = sv64[(j0 + 2) * 2 + ch], v3 = sv64[(j0 + 3) * 2 + ch];
-          if (b1 == b0) { v1 += v0; v0 = 0; }
-          if (b2 == b0) { v2 += v0; v0 = 0; }
-          if (b2 == b1) { v2 += v1; v1 = 0; }
-          if (b3 == b0) { v3 += v0; v0 = 0; }
-          if (b3 == b1) { v3 += v1; v1 = 0; }
-          if (b3 == b2) { v3 += v2; v2 = 0; }
-          i64* p0 = H + (b0 * 32 + lane); i64* p1 = H + (b1 * 32 + lane);
-          i64* p2 = H + (b2 * 32 + lane); i64* p3 = H + (b3 * 32 + lane);
-          const i64 a0 = *p0, a1 = *p1, a2 = *p2, a3 = *p3;
-          *p0 = a0 + v0; *p1 = a1 + v1; *p2 = a2 + v2; *p3 = a3 + v3;
+          for (int j0 = 0; j0 < 32; j0 += 4) {
+            const unsigned c0 = sb8[(j0 + 0) * 16 + fl], c1 = sb8[(j0 + 1) * 16 + fl];
+            const unsigned c2 = sb8[(j0 + 2) * 16 + fl], c3 = sb8[(j0 + 3) * 16 + fl];
+            i64 v0 = sv64[(j0 + 0) * 2 + ch], v1 = sv64[(j0 + 1) * 2 + ch];
+            i64 v2 = sv64[(j0 + 2) * 2 + ch], v3 = sv64[(j0 + 3) * 2 + ch];
+            if (c1 == c0) { v1 += v0; v0 = 0; }
+            if (c2 == c0) { v2 += v0; v0 = 0; }
+            if (c2 == c1) { v2 += v1; v1 = 0; }
+            if (c3 == c0) { v3 += v0; v0 = 0; }
+            if (c3 == c1) { v3 += v1; v1 = 0; }
+            if (c3 == c2) { v3 += v2; v2 = 0; }
+            i64* p0 = H + (c0 * 32 + lane); i64* p1 = H + (c1 * 32 + lane);
+            i64* p2 = H + (c2 * 32 + lane); i64* p3 = H + (c3 * 32 + lane);
+            const i64 a0 = *p0, a1 = *p1, a2 = *p2, a3 = *p3;
+            *p0 = a0 + v0; *p1 = a1 + v1; *p2 = a2 + v2; *p3 = a3 + v3;
+          }
+        } else {
+          for (int j = 0; j < n; ++j) {
+            const unsigned b = sb8[j * 16 + fl];
+            i64* p = H + (b * 32 + lane);
+            *p += sv64[j * 2 + ch];
+          }
         }
-      } else {
-        for (int j = 0; j < n; ++j) {
-          const unsigned b = sb8[j * 16 + fl];
-          i64* p = H + (b * 32 + lane);
-          *p += sv64[j * 2 + ch];
-        }
-      }
-      __syncwarp();
-    }
-    // flush: lane owns column (ch, feature tile*16+fl)
-    const int f = tile * 16 + fl;
-    if (f < V.num_features) {
-      const DevFeat F = V.feats[f];
-      i64* dst = reinterpret_cast<i64*>(out + F.hist_base) + ch;
-      for (int b = 0; b < F.nslots; ++b) {
-        const i64 v = H[b * 32 + lane];
-        if (v) atomic_add_i64(dst + 2 * b, v);
+        __syncwarp();
       }
     }
-    __syncwarp();
+    __syncthreads();
+    // merge the three sub-histograms and flush once: thread tid owns column (tid & 31) of bin rows tid>>5, +8, ...
+    {
+      const int f = tile * 16 + fl;
+      if (f < V.num_features) {
+        const DevFeat F = V.feats[f];
+        i64* dst = reinterpret_cast<i64*>(out + F.hist_base) + ch;
+        for (int b = warp; b < F.nslots; b += HIST_THREADS / 32) {
+          const int e = b * 32 + lane;
+          const i64 v = H0[e] + H1[e] + H2[e];
+          if (v) atomic_add_i64(dst + 2 * b, v);
+        }
+      }
+    }
+    __syncthreads();
   }
-  for (int o = 16; o > 0; o >>= 1) {
-    tg += __shfl_down_sync(0xffffffffu, tg, o);
-    th += __shfl_down_sync(0xffffffffu, th, o);
-  }
-  if (lane == 0 && (tg | th)) {
-    atomic_add_i64(&V.leaves[leaf].tot_g, tg);
-    atomic_add_i64(&V.leaves[leaf].tot_h, th);
-  }
-  if (blockIdx.x == 0 && threadIdx.x == 0) {
+}
+
+// mode: LGBCU_HIST_AUTO (by leaf size), LGBCU_HIST_GLOBAL_ATOMIC, LGBCU_HIST_WARP_PRIVATE
+__device__ void hist_phase(const DevView& V, int leaf, int mode, int min_rows, int bid, int nblocks, unsigned char* smem) {
+  const DevLeaf L = V.leaves[leaf];
+  const DevCtl* c = V.ctl;
+  const bool identity = c->root_identity && leaf == 0 && L.count == V.num_data;
+  const bool small = mode == LGBCU_HIST_GLOBAL_ATOMIC || (mode == LGBCU_HIST_AUTO && L.count < HIST_SMALL_LEAF_ROWS);
+  if (small) hist_global_path(V, L, identity, bid, nblocks);
+  else hist_private_path(V, L, identity, bid, nblocks, min_rows, smem);
+  if (bid == 0 && threadIdx.x == 0) {
     atomicAdd(&V.ctl->prof_hist_calls, 1ull);
     atomicAdd(identity ? &V.ctl->prof_hist_rows : &V.ctl->prof_hist_rows_indexed, (unsigned long long)L.count);
   }
 }
 
+__global__ void __launch_bounds__(HIST_THREADS, 1) k_hist(DevView V, int leaf_arg, int mode, int min_rows) {
+  extern __shared__ __align__(16) unsigned char hist_smem[];
+  int leaf;
+  if (!hist_target(V, leaf_arg, &leaf)) return;
+  hist_phase(V, leaf, mode, min_rows, blockIdx.x, gridDim.x, hist_smem);
+}

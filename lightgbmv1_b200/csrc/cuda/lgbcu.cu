@@ -19,6 +19,7 @@
 #include "split_kernels.cuh"
 #include "partition_kernels.cuh"
 #include "misc_kernels.cuh"
+#include "grow_kernel.cuh"
 
 namespace {
 
@@ -114,6 +115,7 @@ struct LgbCuContext {
   // config
   int hist_mode = LGBCU_HIST_AUTO;
   int hist_min_rows = HIST_MIN_ROWS_PER_WARP;
+  bool persistent_ok = false, use_persistent = false;  // launch-per-phase loop measured faster (profiles/r1_c); LGBCU_PERSISTENT=1 selects k_grow_tree
   int objective = LGBCU_OBJ_NONE; double obj_p[3] = {0, 0, 0};
   int root_count = 0; bool tree_begun = false;
   // profiling
@@ -167,17 +169,7 @@ int ensure_tree_buffers(LgbCuContext* c) {
 
 int launch_hist(LgbCuContext* c, int leaf_arg) {
   const DevView V = c->view();
-  const int mode = c->hist_mode;
-  if (mode == LGBCU_HIST_GLOBAL_ATOMIC || mode == LGBCU_HIST_AUTO) {
-    const int regime = mode == LGBCU_HIST_AUTO ? 1 : 0;
-    // small leaves: enough threads for HIST_SMALL_LEAF_ROWS rows; forced mode: whole-GPU grid
-    const long long work = regime == 1 ? (long long)HIST_SMALL_LEAF_ROWS * c->ntiles16 : (long long)c->N * c->ntiles16;
-    LAUNCH(k_hist_global, grid_for(c, work, 256), 256, 0, c->stream, V, leaf_arg, regime);
-  }
-  if (mode == LGBCU_HIST_WARP_PRIVATE || mode == LGBCU_HIST_AUTO) {
-    const int regime = mode == LGBCU_HIST_AUTO ? 2 : 0;
-    LAUNCH(k_hist_warp_private, c->num_sms, HIST_WARPS_PER_BLOCK * 32, HIST_SMEM_BYTES, c->stream, V, leaf_arg, regime, c->hist_min_rows);
-  }
+  LAUNCH(k_hist, c->num_sms, HIST_THREADS, HIST_SMEM_BYTES, c->stream, V, leaf_arg, c->hist_mode, c->hist_min_rows);
   CU(cudaGetLastError());
   return 0;
 }
@@ -246,7 +238,15 @@ int lgbcu_create(int device_id, LgbCuContext** out) {
   CU(cudaMallocHost(reinterpret_cast<void**>(&c->h_ctl), sizeof(DevCtl)));
   CU(cudaMallocHost(reinterpret_cast<void**>(&c->h_leaf), sizeof(DevLeaf)));
   CU(cudaMallocHost(reinterpret_cast<void**>(&c->h_split), sizeof(DevSplit)));
-  CU(cudaFuncSetAttribute(k_hist_warp_private, cudaFuncAttributeMaxDynamicSharedMemorySize, HIST_SMEM_BYTES));
+  CU(cudaFuncSetAttribute(k_hist, cudaFuncAttributeMaxDynamicSharedMemorySize, HIST_SMEM_BYTES));
+  CU(cudaFuncSetAttribute(k_grow_tree, cudaFuncAttributeMaxDynamicSharedMemorySize, HIST_SMEM_BYTES));
+  {
+    int coop = 0, per_sm = 0;
+    CU(cudaDeviceGetAttribute(&coop, cudaDevAttrCooperativeLaunch, device_id));
+    CU(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, k_grow_tree, GROW_THREADS, HIST_SMEM_BYTES));
+    c->persistent_ok = coop != 0 && per_sm >= 1;
+    if (const char* e = std::getenv("LGBCU_PERSISTENT")) c->use_persistent = std::atoi(e) != 0;
+  }
   *out = c;
   return 0;
 }
@@ -328,8 +328,20 @@ int lgbcu_set_dataset(LgbCuContext* c, int32_t num_data, int32_t num_features, c
                       const LgbCuFeatureMeta* meta) {
   NEED(bins, "lgbcu_set_dataset: bins is NULL");
   if (setup_dataset_common(c, num_data, num_features, meta)) return -1;
-  CU(cudaMemsetAsync(c->d_bins, 0, (size_t)num_data * c->stride, c->stream));
-  CU(cudaMemcpy2DAsync(c->d_bins, c->stride, bins, num_features, num_features, num_data, cudaMemcpyHostToDevice, c->stream));
+  if (c->stride == num_features) {
+    CU(cudaMemcpyAsync(c->d_bins, bins, (size_t)num_data * num_features, cudaMemcpyHostToDevice, c->stream));
+  } else {
+    // one contiguous H2D copy, then pad rows to the 16-byte stride on the device (a strided 2-D copy of 28-byte rows
+    // crawls: one DMA descriptor per row)
+    uint8_t* packed = nullptr;
+    CU(dev_alloc(&packed, (size_t)num_data * num_features));
+    CU(cudaMemcpyAsync(packed, bins, (size_t)num_data * num_features, cudaMemcpyHostToDevice, c->stream));
+    LAUNCH(k_pad_rows, grid_for(c, (long long)num_data * (c->stride / 4), 256), 256, 0, c->stream, (long long)num_data,
+           num_features, c->stride, packed, c->d_bins);
+    CU(cudaGetLastError());
+    CU(cudaStreamSynchronize(c->stream));
+    cudaFree(packed);
+  }
   CU(cudaStreamSynchronize(c->stream));
   return 0;
 }
@@ -725,6 +737,24 @@ int lgbcu_train_tree(LgbCuContext* c, LgbCuSplitRecord* records, int32_t* num_sp
   const int L = c->params.num_leaves;
   const int part_grid = grid_for(c, c->root_count, PART_TILE);
   const bool prof = c->profile;
+  if (c->use_persistent && c->persistent_ok && !c->comm) {
+    // one cooperative launch grows the whole tree (grow_kernel.cuh)
+    DevView Vv = V; int hm = c->hist_mode, mr = c->hist_min_rows, pf = prof ? (std::getenv("LGBCU_PROF_SYNC") ? 2 : 1) : 0;
+    void* args[] = {&Vv, &hm, &mr, &pf};
+    if (prof) CU(cudaMemsetAsync(&c->d_ctl->prof_hist_ns, 0, 9 * sizeof(unsigned long long), c->stream));
+    CU(cudaLaunchCooperativeKernel(reinterpret_cast<void*>(k_grow_tree), dim3(c->num_sms), dim3(GROW_THREADS), args,
+                                   HIST_SMEM_BYTES, c->stream));
+    g_launches.fetch_add(1, std::memory_order_relaxed);
+    CU(cudaMemcpyAsync(c->h_ctl, c->d_ctl, sizeof(DevCtl), cudaMemcpyDeviceToHost, c->stream));
+    CU(cudaMemcpyAsync(c->h_records, c->d_records, sizeof(LgbCuSplitRecord) * (size_t)(L - 1), cudaMemcpyDeviceToHost, c->stream));
+    CU(cudaStreamSynchronize(c->stream));
+    const int n = c->h_ctl->num_splits;
+    NEED(n >= 0 && n <= L - 1, "lgbcu_train_tree: corrupt split count %d", n);
+    std::memcpy(records, c->h_records, sizeof(LgbCuSplitRecord) * (size_t)n);
+    *num_splits = n;
+    if (prof) c->prof_hist_ms += (double)c->h_ctl->prof_hist_ns * 1e-6;
+    return 0;
+  }
   if (prof && (int)c->ev.size() < 2 * L) {
     const size_t old = c->ev.size();
     c->ev.resize(2 * L);
@@ -758,6 +788,15 @@ int lgbcu_train_tree(LgbCuContext* c, LgbCuSplitRecord* records, int32_t* num_sp
   return 0;
 }
 
+int lgbcu_profile_phases(LgbCuContext* c, double* ms8) {
+  NEED(c && ms8, "lgbcu_profile_phases: NULL argument");
+  CU(cudaSetDevice(c->device));
+  CU(cudaMemcpyAsync(c->h_ctl, c->d_ctl, sizeof(DevCtl), cudaMemcpyDeviceToHost, c->stream));
+  CU(cudaStreamSynchronize(c->stream));
+  for (int i = 0; i < 8; ++i) ms8[i] = (double)c->h_ctl->prof_phase_ns[i] * 1e-6;
+  return 0;
+}
+
 int lgbcu_profile_enable(LgbCuContext* c, int on) {
   NEED(c, "lgbcu: NULL context");
   c->profile = on != 0;
@@ -778,7 +817,7 @@ int lgbcu_profile_read(LgbCuContext* c, double* hist_ms, int64_t* hist_calls, do
   if (hist_bytes) *hist_bytes = bytes;
   if (reset) {
     c->prof_hist_ms = 0;
-    CU(cudaMemsetAsync(&c->d_ctl->prof_hist_rows, 0, 3 * sizeof(unsigned long long), c->stream));
+    CU(cudaMemsetAsync(&c->d_ctl->prof_hist_rows, 0, 4 * sizeof(unsigned long long), c->stream));
     CU(cudaStreamSynchronize(c->stream));
   }
   return 0;

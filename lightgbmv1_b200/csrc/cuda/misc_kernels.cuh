@@ -171,6 +171,19 @@ __global__ void k_add_const(int n, double* score, double v) {
   for (int i = blockIdx.x * blockDim.x + threadIdx.x; i < n; i += gridDim.x * blockDim.x) score[i] += v;
 }
 
+// packed [n][F] rows -> padded [n][row_stride] rows (one thread per 4 output bytes)
+__global__ void k_pad_rows(long long n, int F, int row_stride, const uint8_t* __restrict__ src, uint8_t* __restrict__ dst) {
+  const long long words = n * (row_stride / 4);
+  for (long long w = blockIdx.x * (long long)blockDim.x + threadIdx.x; w < words; w += (long long)gridDim.x * blockDim.x) {
+    const long long r = w / (row_stride / 4);
+    const int c = (int)(w - r * (row_stride / 4)) * 4;
+    unsigned v = 0;
+#pragma unroll
+    for (int k = 0; k < 4; ++k) if (c + k < F) v |= (unsigned)src[r * F + c + k] << (8 * k);
+    reinterpret_cast<unsigned*>(dst)[w] = v;
+  }
+}
+
 // column vectors -> row-major matrix (one warp-wide 32-row strip per step; coalesced on the column side)
 __global__ void k_scatter_column(int n, const uint8_t* __restrict__ col, uint8_t* __restrict__ bins, int row_stride,
                                  int f) {

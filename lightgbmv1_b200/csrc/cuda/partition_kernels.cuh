@@ -63,9 +63,8 @@ __device__ __forceinline__ bool goes_left(const SplitRule& r, int bin) {
   return r.maxbin_left;
 }
 
-__global__ void __launch_bounds__(PART_THREADS) k_part_flags(DevView V) {
+__device__ void part_flags_phase(const DevView& V, int bid, int nblocks) {
   const DevCtl* c = V.ctl;
-  if (c->done) return;
   const DevLeaf L = V.leaves[c->split_leaf];
   const DevFeat F = V.feats[c->split_feature];
   const SplitRule rule = make_rule(F, c->split_threshold, c->split_default_left);
@@ -74,7 +73,7 @@ __global__ void __launch_bounds__(PART_THREADS) k_part_flags(DevView V) {
   const int ntiles = (L.count + PART_TILE - 1) / PART_TILE;
   const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
   __shared__ int s_cnt[PART_THREADS / 32];
-  for (int tile = blockIdx.x; tile < ntiles; tile += gridDim.x) {
+  for (int tile = bid; tile < ntiles; tile += nblocks) {
     int lefts = 0;
 #pragma unroll
     for (int r = 0; r < PART_REPS; ++r) {
@@ -101,10 +100,10 @@ __global__ void __launch_bounds__(PART_THREADS) k_part_flags(DevView V) {
   }
 }
 
-// mode 0: training (control step runs); mode 1: step-wise API (only counts/ranges are updated, sums untouched)
-__global__ void __launch_bounds__(1024) k_part_scan(DevView V, int mode) {
+// mode 0: training (control step runs); mode 1: step-wise API (only counts/ranges are updated, sums untouched).
+// One block (any multiple of 32 threads up to 1024).
+__device__ void part_scan_phase(const DevView& V, int mode) {
   DevCtl* c = V.ctl;
-  if (c->done) return;
   const int leaf = c->split_leaf;
   const DevLeaf L = V.leaves[leaf];
   const int ntiles = (L.count + PART_TILE - 1) / PART_TILE;
@@ -117,7 +116,8 @@ __global__ void __launch_bounds__(1024) k_part_scan(DevView V, int mode) {
   const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
   if (threadIdx.x == 0) s_carry = 0;
   __syncthreads();
-  for (int base = 0; base < ntiles; base += 1024) {
+  const int nthreads = blockDim.x;
+  for (int base = 0; base < ntiles; base += nthreads) {
     const int i = base + threadIdx.x;
     const int v = i < ntiles ? V.tile_left[i] : 0;
     int inc = v;
@@ -128,7 +128,7 @@ __global__ void __launch_bounds__(1024) k_part_scan(DevView V, int mode) {
     if (lane == 31) s_warp[warp] = inc;
     __syncthreads();
     if (warp == 0) {
-      int w = s_warp[lane];
+      int w = lane < nthreads / 32 ? s_warp[lane] : 0;
       int winc = w;
       for (int o = 1; o < 32; o <<= 1) {
         const int x = __shfl_up_sync(0xffffffffu, winc, o);
@@ -140,7 +140,7 @@ __global__ void __launch_bounds__(1024) k_part_scan(DevView V, int mode) {
     const int excl = s_carry + s_warp[warp] + inc - v;
     if (i < ntiles) V.tile_left[i] = excl;
     __syncthreads();
-    if (threadIdx.x == 1023) s_carry = excl + v;
+    if (threadIdx.x == nthreads - 1) s_carry = excl + v;
     __syncthreads();
   }
   if (threadIdx.x != 0) return;
@@ -199,10 +199,8 @@ __global__ void __launch_bounds__(1024) k_part_scan(DevView V, int mode) {
   if (c->num_leaves >= V.p.num_leaves) c->done = 2;  // tree is full; nothing more to enqueue
 }
 
-__global__ void __launch_bounds__(PART_THREADS) k_part_scatter(DevView V, int parent_buf_arg) {
+__device__ void part_scatter_phase(const DevView& V, int bid, int nblocks) {
   const DevCtl* c = V.ctl;
-  // done == 2 is set by the k_part_scan that just ran for the LAST split: its scatter must still happen
-  if (c->done == 1) return;
   const int leaf = c->split_leaf;
   const DevLeaf A = V.leaves[leaf];  // already the left child: begin unchanged, buf flipped
   const int left_total = c->split_left_count;
@@ -211,8 +209,7 @@ __global__ void __launch_bounds__(PART_THREADS) k_part_scatter(DevView V, int pa
   int* dst = V.indices[A.buf] + A.begin;
   const int ntiles = (count + PART_TILE - 1) / PART_TILE;
   const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
-  (void)parent_buf_arg;
-  for (int tile = blockIdx.x; tile < ntiles; tile += gridDim.x) {
+  for (int tile = bid; tile < ntiles; tile += nblocks) {
     // every warp redundantly scans the tile's 32 ballot words (no block sync needed)
     const unsigned myword = V.part_bits[(size_t)tile * (PART_TILE / 32) + lane];
     const int pc = __popc(myword);
@@ -241,4 +238,20 @@ __global__ void __launch_bounds__(PART_THREADS) k_part_scatter(DevView V, int pa
       }
     }
   }
+}
+
+// stand-alone launches (step-wise API and the non-persistent training loop)
+__global__ void __launch_bounds__(PART_THREADS) k_part_flags(DevView V) {
+  if (V.ctl->done) return;
+  part_flags_phase(V, blockIdx.x, gridDim.x);
+}
+__global__ void __launch_bounds__(1024) k_part_scan(DevView V, int mode) {
+  if (V.ctl->done) return;
+  part_scan_phase(V, mode);
+}
+__global__ void __launch_bounds__(PART_THREADS) k_part_scatter(DevView V, int unused) {
+  // done == 2 is set by the k_part_scan that just ran for the LAST split: its scatter must still happen
+  if (V.ctl->done == 1) return;
+  (void)unused;
+  part_scatter_phase(V, blockIdx.x, gridDim.x);
 }

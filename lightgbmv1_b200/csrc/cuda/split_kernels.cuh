@@ -308,22 +308,15 @@ __device__ __forceinline__ bool split_better(double ga, int fa, double gb, int f
   return fa < fb;
 }
 
-// mode 0: training (smaller/larger from DevCtl, control step at the end);
-// mode 1: explicit single leaf, no control (step-wise API / tests).
-// grid = (num_features, 2): blockIdx.y = 0 scans the smaller leaf, 1 forms larger = parent - smaller and scans it.
-__global__ void __launch_bounds__(FS_THREADS) k_find_split(DevView V, int mode, int leaf_arg) {
-  __shared__ ScanSmem S;
-  __shared__ int s_last;
+// FixHistogram / Subtract / FindBestThreshold of ONE (feature, leaf) pair by one block of FS_THREADS threads.
+// sel = 0: the smaller leaf; sel = 1: the larger leaf (= parent - smaller, formed here, in the parent's slot).
+__device__ void find_item(const DevView& V, ScanSmem& S, int f, int sel, int smaller, int larger) {
   DevCtl* c = V.ctl;
-  if (mode == 0 && c->done) return;
-  const int f = blockIdx.x, sel = blockIdx.y;
-  const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
-  const bool active = (mode == 1) || !c->skip_find;
-  const int smaller = (mode == 1) ? leaf_arg : c->smaller;
-  const int larger = (mode == 1) ? -1 : c->larger;
+  const int tid = threadIdx.x;
   const int my_leaf = sel == 0 ? smaller : larger;
+  if (my_leaf < 0 || f >= V.num_features) return;
+  {
 
-  if (active && my_leaf >= 0 && f < V.num_features) {
     const DevFeat F = V.feats[f];
     const DevLeaf Ls = V.leaves[smaller];
     int used = V.feat_used[f] != 0;
@@ -401,19 +394,15 @@ __global__ void __launch_bounds__(FS_THREADS) k_find_split(DevView V, int mode, 
         if (used) V.splittable[(size_t)Ll.slot * V.num_features + f] = (int8_t)sp;
       }
     }
-  }
+    }
+  __syncthreads();  // S is reused by the caller's next item
+}
 
-  // ---- last block: reduce over features, then choose the next leaf to split ----
-  __threadfence();
-  __syncthreads();
-  if (threadIdx.x == 0) {
-    const unsigned ticket = atomicAdd(&c->feat_done, 1u);
-    s_last = (ticket == gridDim.x * gridDim.y - 1);
-  }
-  __syncthreads();
-  if (!s_last) return;
-  __threadfence();
-  if (warp != 0) return;
+// Reduce the per-feature candidates of the two scanned leaves (SplitInfo::operator>), then pick the next leaf to
+// split (ArgMax over best_split_per_leaf_) and publish the split descriptor.  One warp.
+__device__ void find_control(const DevView& V, int mode, bool active, int smaller, int larger) {
+  DevCtl* c = V.ctl;
+  const int lane = threadIdx.x & 31;
   if (active) {
     for (int sel = 0; sel < 2; ++sel) {
       const int leaf = sel == 0 ? smaller : larger;
@@ -439,7 +428,6 @@ __global__ void __launch_bounds__(FS_THREADS) k_find_split(DevView V, int mode, 
     }
   }
   __syncwarp();
-  if (lane == 0) c->feat_done = 0;
   if (mode != 0) return;
   __threadfence_block();
   // ArrayArgs<SplitInfo>::ArgMax(best_split_per_leaf_): first leaf with the best (gain, feature)
@@ -473,18 +461,49 @@ __global__ void __launch_bounds__(FS_THREADS) k_find_split(DevView V, int mode, 
   }
 }
 
+// mode 0: training (smaller/larger from DevCtl, control step at the end);
+// mode 1: explicit single leaf, no control (step-wise API / tests).
+// grid = (num_features, 2): blockIdx.y = 0 scans the smaller leaf, 1 forms larger = parent - smaller and scans it.
+// The last block to finish runs the control step.
+__global__ void __launch_bounds__(FS_THREADS) k_find_split(DevView V, int mode, int leaf_arg) {
+  __shared__ ScanSmem S;
+  __shared__ int s_last;
+  DevCtl* c = V.ctl;
+  if (mode == 0 && c->done) return;
+  const bool active = (mode == 1) || !c->skip_find;
+  const int smaller = (mode == 1) ? leaf_arg : c->smaller;
+  const int larger = (mode == 1) ? -1 : c->larger;
+  if (active) find_item(V, S, blockIdx.x, blockIdx.y, smaller, larger);
+  __threadfence();
+  __syncthreads();
+  if (threadIdx.x == 0) {
+    const unsigned ticket = atomicAdd(&c->feat_done, 1u);
+    s_last = (ticket == gridDim.x * gridDim.y - 1);
+  }
+  __syncthreads();
+  if (!s_last) return;
+  __threadfence();
+  if (threadIdx.x >= 32) return;
+  if (threadIdx.x == 0) c->feat_done = 0;
+  find_control(V, mode, active, smaller, larger);
+}
+
 // Root LeafSplits::Init (leaf_splits.hpp:66-79; all-reduced over ranks in data_parallel_tree_learner.cpp:126-151):
 // sum over every stored value of feature 0 of the (already rank-reduced) root histogram -- exact in fixed point.
-__global__ void k_root_sums(DevView V) {
+__device__ void root_sums_warp(const DevView& V) {  // one warp
   const DevCtl* c = V.ctl;
   DevLeaf* L = &V.leaves[0];
   const DevFeat F = V.feats[0];
   const HistEntry* h = V.pool + (size_t)L->slot * V.total_bin + F.hist_base;
+  const int lane = threadIdx.x & 31;
   i64 g = 0, hh = 0;
-  for (int s = threadIdx.x; s < F.nslots; s += 32) { g += h[s].g; hh += h[s].h; }
+  for (int s = lane; s < F.nslots; s += 32) { g += h[s].g; hh += h[s].h; }
   g = warp_sum(g); hh = warp_sum(hh);
-  if (threadIdx.x == 0) {
+  if (lane == 0) {
     L->sum_g = (double)g * c->inv_g;
     L->sum_h = (double)hh * c->inv_h;
   }
+}
+__global__ void k_root_sums(DevView V) {
+  if (threadIdx.x < 32) root_sums_warp(V);
 }

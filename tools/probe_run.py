@@ -14,3 +14,4 @@ for rep in range(3):
     t = time.time(); recs = L.train_tree(); dt = time.time() - t
     ms, calls, nbytes = L.profile_read()
 print(f"min_rows={os.environ.get('LGBCU_HIST_MIN_ROWS')}: tree {dt*1e3:.2f} ms, hist {ms:.2f} ms, {nbytes/ms/1e6:.1f} GB/s")
+print("phases ms [hist, root, find, control, flags, scan, scatter]:", [round(x, 3) for x in L.profile_phases()[:8]])
