@@ -107,6 +107,26 @@ __device__ __forceinline__ void chain2(const double* __restrict__ g, const doubl
   *ag_io = ag; *ah_io = ah;
 }
 template <int DIR>
+__device__ __forceinline__ void chain1(const double* __restrict__ h, double* oh, int t_first, int t_last, int skip_t,
+                                       double sign, double* ah_io) {
+  double ah = *ah_io;
+  const int count = DIR > 0 ? t_last - t_first + 1 : t_first - t_last + 1;
+  for (int base = 0; base < count; base += 8) {
+    double vh[8];
+#pragma unroll
+    for (int k = 0; k < 8; ++k) {
+      const int t = t_first + DIR * (base + k);
+      vh[k] = ((base + k) < count && t != skip_t) ? sign * h[t] : 0.0;
+    }
+#pragma unroll
+    for (int k = 0; k < 8; ++k) {
+      ah += vh[k];
+      if (oh && (base + k) < count) oh[t_first + DIR * (base + k)] = ah;
+    }
+  }
+  *ah_io = ah;
+}
+template <int DIR>
 __device__ __forceinline__ void chain_cnt(const int* __restrict__ c, int* out, int t_first, int t_last, int skip_t,
                                           int sign, int* acc_io) {
   int acc = *acc_io;
@@ -133,7 +153,8 @@ __device__ __forceinline__ void chain_cnt(const int* __restrict__ c, int* out, i
 // Shared-memory work area of one (feature, leaf) block.
 struct ScanSmem {
   double gd[256], hd[256];      // data_[t] as doubles (after FixHistogram)
-  double sgd[256], shd[256];    // the smaller leaf's entries (larger-leaf blocks: needed to redo its FixHistogram)
+  i64 gi[256];                  // gradient entries in fixed point (exact prefix / suffix sums)
+  i64 wtot[4][FS_WARPS];        // per-warp totals of the block-wide integer scans / reductions
   double RG[256], RH[256];      // reverse scan: sum_right_gradient / sum_right_hessian after adding bin t
   double LG[256], LH[256];      // forward scan: sum_left_* after adding bin t
   int cnt[256], RC[256], LC[256];
@@ -142,15 +163,49 @@ struct ScanSmem {
   int wsplit[FS_WARPS];
 };
 
-// FindBestThreshold for one numerical feature, one block.  The floating-point accumulations of the reference
-// (FixHistogram's sequential subtraction and the two sequential scans that start from kEpsilon) are replayed in the
-// reference's order by four single threads on four different warps -- each chain is <= 256 dependent DADDs -- so that
-// whenever the histogram entries themselves are exact (always the case for the leaves where ties occur) every sum
-// that enters a gain is bit-identical to the reference's.  Gains (two fp64 divisions per threshold) are then
-// evaluated one threshold per thread and reduced with the reference's tie rules.
+// block-wide sum of one int64 per thread (all FS_THREADS threads call; result broadcast)
+__device__ __forceinline__ i64 block_sum_i64(i64 v, i64* wtot) {
+  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+  v = warp_sum(v);
+  if (lane == 0) wtot[warp] = v;
+  __syncthreads();
+  i64 t = 0;
+#pragma unroll
+  for (int w = 0; w < FS_WARPS; ++w) t += wtot[w];
+  __syncthreads();
+  return t;
+}
+// inclusive prefix (DIR=+1: over lower thread ids) or suffix (DIR=-1: over higher thread ids) sum across the block
+template <int DIR>
+__device__ __forceinline__ i64 block_scan_i64(i64 v, i64* wtot) {
+  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+  i64 inc = v;
+#pragma unroll
+  for (int o = 1; o < 32; o <<= 1) {
+    const i64 x = DIR > 0 ? __shfl_up_sync(FULL_MASK, inc, o) : __shfl_down_sync(FULL_MASK, inc, o);
+    if (DIR > 0 ? lane >= o : lane + o < 32) inc += x;
+  }
+  if (DIR > 0 ? lane == 31 : lane == 0) wtot[warp] = inc;
+  __syncthreads();
+  i64 off = 0;
+#pragma unroll
+  for (int w = 0; w < FS_WARPS; ++w) if (DIR > 0 ? w < warp : w > warp) off += wtot[w];
+  __syncthreads();
+  return inc + off;
+}
+
+// FindBestThreshold for one numerical feature, one block.
+// Arithmetic fidelity.  The reference accumulates bins sequentially in double.  Where its running sums are exactly
+// representable (always for the small / medium leaves where gains tie) a sequential sum equals the exact sum, so
+// gradient sums, FixHistogram's residual and the implicit first bin are formed from exact 64-bit integer
+// prefix/suffix sums in parallel and rounded once.  The hessian scans are different: they start from kEpsilon
+// (1e-15f), whose low bits are rounded away step by step as the sum grows, so their value depends on the ORDER of
+// additions; those two chains (<= 256 dependent DADDs each) are replayed in the reference's order by one thread
+// each, with operands prefetched so that only the DADD latency is on the critical path.  Gains (two fp64 divisions
+// per threshold) are then evaluated one threshold per thread and reduced with the reference's tie rules.
 __device__ void scan_feature_block(ScanSmem& S, int nt, const DevFeat& F, double sum_g, double leaf_sum_h,
-                                   int num_data, double parent_output, const DevParams& P, DevSplit* out,
-                                   int* splittable_out) {
+                                   int num_data, double parent_output, const DevParams& P, double inv_g_in,
+                                   DevSplit* out, int* splittable_out) {
   const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
   const double sum_h = leaf_sum_h + (double)(2 * 1e-15f);  // FindBestThreshold: sum_hessian + 2 * kEpsilon
   const double cnt_factor = num_data / sum_h;
@@ -164,23 +219,40 @@ __device__ void scan_feature_block(ScanSmem& S, int nt, const DevFeat& F, double
   const int t_end = nt - 2;                                            // forward range [0, t_end]
 
   S.cnt[tid] = (tid < nt) ? round_int(S.hd[tid] * cnt_factor) : 0;
+  const int skip_t = skip_default ? (int)F.default_bin - offset : -1000;  // data_ index of the skipped default bin
+  const double inv_g = inv_g_in;
+  // gradient sums: exact integer suffix (reverse scan) / prefix (forward scan) sums, one rounding each
+  const bool in_rev = tid >= t_lo && tid <= t_hi && tid != skip_t;
+  const bool in_fwd = two_way && tid <= t_end && tid != skip_t;
+  const i64 my_gi = S.gi[tid];
+  const i64 rev_gi = block_scan_i64<-1>(in_rev ? my_gi : 0, S.wtot[0]);
+  S.RG[tid] = (double)rev_gi * inv_g;
+  if (two_way) {
+    const i64 fwd_gi = block_scan_i64<1>(in_fwd ? my_gi : 0, S.wtot[1]);
+    double base_g = 0.0;
+    if (implicit_first) {
+      const i64 all_g = block_sum_i64(tid < nt ? my_gi : 0, S.wtot[2]);
+      base_g = sum_g - (double)all_g * inv_g;
+    }
+    S.LG[tid] = base_g + (double)fwd_gi * inv_g;
+    if (tid == 0) S.base_g = base_g;
+  }
   __syncthreads();
   // ---- four sequential chains on four warps
-  const int skip_t = skip_default ? (int)F.default_bin - offset : -1000;  // data_ index of the skipped default bin
-  if (tid == 0) {  // reverse sums
-    double ag = 0.0f, ah = LGB_EPS;
-    chain2<-1>(S.gd, S.hd, S.RG, S.RH, t_hi, t_lo, skip_t, 1.0, &ag, &ah);
+  if (tid == 0) {  // reverse hessian chain (starts from kEpsilon: order matters)
+    double ah = LGB_EPS;
+    chain1<-1>(S.hd, S.RH, t_hi, t_lo, skip_t, 1.0, &ah);
   } else if (tid == 32) {  // reverse counts
     int ac = 0;
     chain_cnt<-1>(S.cnt, S.RC, t_hi, t_lo, skip_t, 1, &ac);
-  } else if (tid == 64 && two_way) {  // forward sums
-    double lg = 0.0f, lh = LGB_EPS;
+  } else if (tid == 64 && two_way) {  // forward hessian chain
+    double lh = LGB_EPS;
     if (implicit_first) {
-      lg = sum_g; lh = sum_h - LGB_EPS;
-      chain2<1>(S.gd, S.hd, nullptr, nullptr, 0, nt - 1, -1000, -1.0, &lg, &lh);
+      lh = sum_h - LGB_EPS;
+      chain1<1>(S.hd, nullptr, 0, nt - 1, -1000, -1.0, &lh);
     }
-    S.base_g = lg; S.base_h = lh;
-    chain2<1>(S.gd, S.hd, S.LG, S.LH, 0, t_end, skip_t, 1.0, &lg, &lh);
+    S.base_h = lh;
+    chain1<1>(S.hd, S.LH, 0, t_end, skip_t, 1.0, &lh);
   } else if (tid == 96 && two_way) {  // forward counts
     int lc = 0;
     if (implicit_first) {
@@ -333,20 +405,27 @@ __device__ void find_item(const DevView& V, ScanSmem& S, int f, int sel, int sma
       if (used) {
         HistEntry e; e.g = 0; e.h = 0;
         if (tid < nt) e = hs[1 + tid];
-        S.gd[tid] = (double)e.g * inv_g; S.hd[tid] = (double)e.h * inv_h;
-        __syncthreads();
         if (F.mfb > 0) {
-          // Dataset::FixHistogram (dataset.cpp:1410-1428), in the reference's order and precision
-          if (tid == 0) {
-            double vg = Ls.sum_g, vh = Ls.sum_h;
-            chain2<1>(S.gd, S.hd, nullptr, nullptr, 0, F.num_bin - 1, F.mfb, -1.0, &vg, &vh);
-            S.gd[F.mfb] = vg; S.hd[F.mfb] = vh;
+          // Dataset::FixHistogram (dataset.cpp:1410-1428): data[mfb] = leaf sum - sum of the other bins.  Every
+          // step of the reference's sequential subtraction is exact while the bins are (the running value only
+          // shrinks), so one subtraction of the exact integer sum gives the same double, residue included.
+          const bool other = tid < nt && tid != F.mfb;
+          const i64 og = block_sum_i64(other ? e.g : 0, S.wtot[0]);
+          const i64 oh = block_sum_i64(other ? e.h : 0, S.wtot[1]);
+          const double vg = Ls.sum_g - (double)og * inv_g, vh = Ls.sum_h - (double)oh * inv_h;
+          if (tid == F.mfb) {
+            e = hs[0];  // exact integer twin of the most-frequent bin (rows stored as 0)
+            hs[1 + F.mfb] = e;
             *fix_s = make_double2(vg, vh);
-            hs[1 + F.mfb] = hs[0];  // exact integer twin, used by later subtractions / exports
           }
-          __syncthreads();
+          S.gd[tid] = tid == F.mfb ? vg : (double)e.g * inv_g;
+          S.hd[tid] = tid == F.mfb ? vh : (double)e.h * inv_h;
+        } else {
+          S.gd[tid] = (double)e.g * inv_g; S.hd[tid] = (double)e.h * inv_h;
         }
-        scan_feature_block(S, nt, F, Ls.sum_g, Ls.sum_h, Ls.gcount, parent_output_of(Ls, smaller, V.p), V.p, &o, &sp);
+        S.gi[tid] = e.g;
+        __syncthreads();
+        scan_feature_block(S, nt, F, Ls.sum_g, Ls.sum_h, Ls.gcount, parent_output_of(Ls, smaller, V.p), V.p, inv_g, &o, &sp);
         o.feature = f; o.real_feature = F.real_index;
       }
       if (tid == 0) {
@@ -361,7 +440,9 @@ __device__ void find_item(const DevView& V, ScanSmem& S, int f, int sel, int sma
         HistEntry e; e.g = 0; e.h = 0; HistEntry b; b.g = 0; b.h = 0;
         if (tid < nt) {
           const HistEntry a = hl[1 + tid];
-          b = hs[1 + tid];
+          // the smaller leaf's most-frequent-bin entry is being written by the sibling block: take its exact twin
+          // (stored value 0) instead of racing on it
+          b = (F.mfb > 0 && tid == F.mfb) ? hs[0] : hs[1 + tid];
           e.g = a.g - b.g; e.h = a.h - b.h;  // FeatureHistogram::Subtract, exact
           hl[1 + tid] = e;
         }
@@ -370,23 +451,25 @@ __device__ void find_item(const DevView& V, ScanSmem& S, int f, int sel, int sma
           HistEntry e0; e0.g = a0.g - b0.g; e0.h = a0.h - b0.h;
           hl[0] = e0;
         }
-        S.gd[tid] = (double)e.g * inv_g; S.hd[tid] = (double)e.h * inv_h;
-        S.sgd[tid] = (double)b.g * inv_g; S.shd[tid] = (double)b.h * inv_h;
-        __syncthreads();
         if (F.mfb > 0) {
-          // larger.data[mfb] = parent.data[mfb] (fixed when the parent was scanned) - smaller.data[mfb] (fixed now);
-          // the smaller leaf's FixHistogram is redone here so that this block does not wait for its sibling block
-          if (tid == 0) {
-            double vg = Ls.sum_g, vh = Ls.sum_h;
-            chain2<1>(S.sgd, S.shd, nullptr, nullptr, 0, F.num_bin - 1, F.mfb, -1.0, &vg, &vh);
-            const double2 pf = *fix_l;
-            const double lg = pf.x - vg, lh = pf.y - vh;
-            S.gd[F.mfb] = lg; S.hd[F.mfb] = lh;
-            *fix_l = make_double2(lg, lh);
-          }
-          __syncthreads();
+          // larger.data[mfb] = parent.data[mfb] (fixed when the parent was scanned) - smaller.data[mfb] (fixed now; the
+          // smaller leaf's FixHistogram is redone here so that this block does not wait for its sibling block)
+          const bool other = tid < nt && tid != F.mfb;
+          const i64 og = block_sum_i64(other ? b.g : 0, S.wtot[0]);
+          const i64 oh = block_sum_i64(other ? b.h : 0, S.wtot[1]);
+          const double sg_fix = Ls.sum_g - (double)og * inv_g, sh_fix = Ls.sum_h - (double)oh * inv_h;
+          const double2 pf = *fix_l;
+          const double lg = pf.x - sg_fix, lh = pf.y - sh_fix;
+          __syncthreads();  // every thread has read *fix_l
+          if (tid == F.mfb) *fix_l = make_double2(lg, lh);
+          S.gd[tid] = tid == F.mfb ? lg : (double)e.g * inv_g;
+          S.hd[tid] = tid == F.mfb ? lh : (double)e.h * inv_h;
+        } else {
+          S.gd[tid] = (double)e.g * inv_g; S.hd[tid] = (double)e.h * inv_h;
         }
-        scan_feature_block(S, nt, F, Ll.sum_g, Ll.sum_h, Ll.gcount, parent_output_of(Ll, larger, V.p), V.p, &o, &sp);
+        S.gi[tid] = e.g;
+        __syncthreads();
+        scan_feature_block(S, nt, F, Ll.sum_g, Ll.sum_h, Ll.gcount, parent_output_of(Ll, larger, V.p), V.p, inv_g, &o, &sp);
         o.feature = f; o.real_feature = F.real_index;
       }
       if (tid == 0) {
