@@ -40,6 +40,12 @@ struct DevSplit {    // SplitInfo, POD
   double left_sum_g, left_sum_h, right_sum_g, right_sum_h;
 };
 
+struct __align__(16) SplitKey {  // what SplitInfo::operator> compares: compact twin of a DevSplit for arg-max passes
+  double gain;
+  int real_feature;
+  int pad;
+};
+
 struct DevLeaf {     // DataPartition range + LeafSplits + pool slot of one leaf
   int begin, count;  // range in indices[buf]
   int slot;          // histogram pool slot
@@ -94,6 +100,8 @@ struct DevView {
   DevLeaf* leaves;
   DevSplit* best;            // best_split_per_leaf_
   DevSplit* feat_best;       // [2][num_features] per-feature candidates of (smaller, larger)
+  SplitKey* feat_key;        // [2][num_features] (gain, real feature) of feat_best, 16 B each: coalesced arg-max
+  SplitKey* leaf_key;        // [num_leaves]      (gain, real feature) of best
   DevCtl* ctl;
   LgbCuSplitRecord* records;
   int* tile_left;            // partition scratch: lefts per 1024-row tile, then exclusive offsets

@@ -99,6 +99,7 @@ struct LgbCuContext {
   int8_t* d_splittable = nullptr; int8_t* d_parent_split = nullptr; double2* d_mfb_fix = nullptr;
   DevLeaf* d_leaves = nullptr;
   DevSplit *d_best = nullptr, *d_feat_best = nullptr;
+  SplitKey *d_feat_key = nullptr, *d_leaf_key = nullptr;
   DevCtl* d_ctl = nullptr;
   LgbCuSplitRecord* d_records = nullptr;
   double* d_leaf_value = nullptr;
@@ -115,6 +116,7 @@ struct LgbCuContext {
   // config
   int hist_mode = LGBCU_HIST_AUTO;
   int hist_min_rows = HIST_MIN_ROWS_PER_WARP;
+  cudaGraphExec_t tree_graph = nullptr; bool use_graph = true;  // the per-tree launch sequence, captured once
   bool persistent_ok = false, use_persistent = false;  // launch-per-phase loop measured faster (profiles/r1_c); LGBCU_PERSISTENT=1 selects k_grow_tree
   int objective = LGBCU_OBJ_NONE; double obj_p[3] = {0, 0, 0};
   int root_count = 0; bool tree_begun = false;
@@ -129,7 +131,7 @@ struct LgbCuContext {
     V.bins = d_bins; V.feats = d_feats; V.feat_used = d_feat_used; V.splittable = d_splittable;
     V.parent_split = d_parent_split; V.mfb_fix = d_mfb_fix;
     V.grad = d_grad; V.hess = d_hess; V.indices[0] = d_indices[0]; V.indices[1] = d_indices[1];
-    V.pool = d_pool; V.leaves = d_leaves; V.best = d_best; V.feat_best = d_feat_best; V.ctl = d_ctl;
+    V.pool = d_pool; V.leaves = d_leaves; V.best = d_best; V.feat_best = d_feat_best; V.feat_key = d_feat_key; V.leaf_key = d_leaf_key; V.ctl = d_ctl;
     V.records = d_records; V.tile_left = d_tile_left; V.part_bits = d_part_bits; V.p = params;
     V.data_parallel = comm != nullptr ? 1 : 0;
     return V;
@@ -146,11 +148,16 @@ int grid_for(const LgbCuContext* c, long long work, int block, int per_sm = 8) {
   return (int)g;
 }
 
+void drop_graph(LgbCuContext* c) {
+  if (c->tree_graph) { cudaGraphExecDestroy(c->tree_graph); c->tree_graph = nullptr; }
+}
+
 int ensure_tree_buffers(LgbCuContext* c) {
   NEED(c->F > 0 && c->N > 0, "lgbcu: dataset not set");
   NEED(c->params_set, "lgbcu: tree params not set");
   const int L = c->params.num_leaves;
   if (c->alloc_leaves == L && c->d_pool) return 0;
+  drop_graph(c);
   CU(cudaSetDevice(c->device));
   CU(dev_alloc(&c->d_pool, (size_t)L * c->total_bin));
   CU(dev_alloc(&c->d_splittable, (size_t)L * c->F));
@@ -158,6 +165,7 @@ int ensure_tree_buffers(LgbCuContext* c) {
   CU(cudaMemsetAsync(c->d_mfb_fix, 0, sizeof(double2) * (size_t)L * c->F, c->stream));
   CU(dev_alloc(&c->d_leaves, (size_t)L));
   CU(dev_alloc(&c->d_best, (size_t)L));
+  CU(dev_alloc(&c->d_leaf_key, (size_t)L));
   CU(dev_alloc(&c->d_records, (size_t)L));
   CU(dev_alloc(&c->d_leaf_value, (size_t)L));
   if (c->h_records) cudaFreeHost(c->h_records);
@@ -246,6 +254,7 @@ int lgbcu_create(int device_id, LgbCuContext** out) {
     CU(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, k_grow_tree, GROW_THREADS, HIST_SMEM_BYTES));
     c->persistent_ok = coop != 0 && per_sm >= 1;
     if (const char* e = std::getenv("LGBCU_PERSISTENT")) c->use_persistent = std::atoi(e) != 0;
+    if (const char* e = std::getenv("LGBCU_GRAPH")) c->use_graph = std::atoi(e) != 0;
   }
   *out = c;
   return 0;
@@ -255,12 +264,13 @@ int lgbcu_destroy(LgbCuContext* c) {
   if (!c) return 0;
   cudaSetDevice(c->device);
   cudaStreamSynchronize(c->stream);
+  drop_graph(c);
   lgbcu_comm_destroy(c);
   void* ptrs[] = {c->d_bins, c->d_feats, c->d_feat_used, c->d_grad, c->d_hess, c->d_label, c->d_weight, c->d_score,
                   c->d_indices[0], c->d_indices[1], c->d_part_bits, c->d_tile_left, c->d_query, c->d_label_gain,
                   c->d_inv_max_dcg, c->d_sigmoid_table, c->d_pool, c->d_splittable, c->d_leaves, c->d_best,
                   c->d_feat_best, c->d_ctl, c->d_records, c->d_leaf_value, c->d_export, c->d_tree_i32, c->d_tree_i8,
-                  c->d_tree_f64, c->d_rows, c->d_scratch, c->d_parent_split, c->d_mfb_fix};
+                  c->d_tree_f64, c->d_rows, c->d_scratch, c->d_parent_split, c->d_mfb_fix, c->d_feat_key, c->d_leaf_key};
   for (void* p : ptrs) if (p) cudaFree(p);
   if (c->h_records) cudaFreeHost(c->h_records);
   if (c->h_ctl) cudaFreeHost(c->h_ctl);
@@ -306,6 +316,7 @@ static int setup_dataset_common(LgbCuContext* c, int32_t num_data, int32_t num_f
   CU(dev_alloc(&c->d_feat_used, (size_t)num_features));
   CU(cudaMemsetAsync(c->d_feat_used, 1, num_features, c->stream));
   CU(dev_alloc(&c->d_feat_best, (size_t)2 * num_features));
+  CU(dev_alloc(&c->d_feat_key, (size_t)2 * num_features));
   CU(dev_alloc(&c->d_parent_split, (size_t)num_features));
   CU(cudaMemsetAsync(c->d_parent_split, 1, num_features, c->stream));
   CU(dev_alloc(&c->d_grad, (size_t)num_data));
@@ -319,6 +330,7 @@ static int setup_dataset_common(LgbCuContext* c, int32_t num_data, int32_t num_f
   CU(dev_alloc(&c->d_part_bits, ntiles * (PART_TILE / 32)));
   CU(dev_alloc(&c->d_export, (size_t)2 * c->total_bin));
   c->alloc_leaves = 0;  // pool depends on total_bin
+  drop_graph(c);
   c->has_label = c->has_weight = false;
   c->tree_begun = false;
   return 0;
@@ -375,6 +387,7 @@ int lgbcu_set_tree_params(LgbCuContext* c, const LgbCuTreeParams* p) {
   d.min_gain_to_split = p->min_gain_to_split; d.max_delta_step = p->max_delta_step; d.path_smooth = p->path_smooth;
   d.use_l1 = p->lambda_l1 > 0; d.use_max_output = p->max_delta_step > 0; d.use_smoothing = p->path_smooth > LGB_EPS;
   c->params = d; c->params_set = true;
+  drop_graph(c);  // kernel arguments (DevParams) are baked into the captured graph
   return 0;
 }
 
@@ -382,6 +395,7 @@ int lgbcu_set_hist_mode(LgbCuContext* c, int mode) {
   NEED(c, "lgbcu: NULL context");
   NEED(mode >= 0 && mode <= 2, "lgbcu_set_hist_mode: unknown mode %d", mode);
   c->hist_mode = mode;
+  drop_graph(c);
   return 0;
 }
 
@@ -753,6 +767,37 @@ int lgbcu_train_tree(LgbCuContext* c, LgbCuSplitRecord* records, int32_t* num_sp
     std::memcpy(records, c->h_records, sizeof(LgbCuSplitRecord) * (size_t)n);
     *num_splits = n;
     if (prof) c->prof_hist_ms += (double)c->h_ctl->prof_hist_ns * 1e-6;
+    return 0;
+  }
+  if (c->use_graph && !prof && !c->comm) {
+    // the launch sequence of a tree is fixed (all sizes are read on the device): capture it once, replay per tree
+    if (!c->tree_graph) {
+      cudaGraph_t g = nullptr;
+      CU(cudaStreamBeginCapture(c->stream, cudaStreamCaptureModeThreadLocal));
+      bool ok = true;
+      for (int s = 0; s < L - 1 && ok; ++s) {
+        ok = launch_hist(c, -1) == 0;
+        if (s == 0) LAUNCH(k_root_sums, 1, 32, 0, c->stream, V);
+        LAUNCH(k_find_split, dim3(c->F, 2), FS_THREADS, 0, c->stream, V, 0, -1);
+        LAUNCH(k_part_flags, part_grid, PART_THREADS, 0, c->stream, V);
+        LAUNCH(k_part_scan, 1, 1024, 0, c->stream, V, 0);
+        LAUNCH(k_part_scatter, part_grid, PART_THREADS, 0, c->stream, V, 0);
+      }
+      cudaError_t ce = cudaStreamEndCapture(c->stream, &g);
+      if (!ok || ce != cudaSuccess || !g) { if (g) cudaGraphDestroy(g); return fail("lgbcu_train_tree: graph capture failed (%s)", cudaGetErrorString(ce)); }
+      ce = cudaGraphInstantiate(&c->tree_graph, g, 0);
+      cudaGraphDestroy(g);
+      if (ce != cudaSuccess) { c->tree_graph = nullptr; return fail("lgbcu_train_tree: graph instantiate failed (%s)", cudaGetErrorString(ce)); }
+    }
+    CU(cudaGraphLaunch(c->tree_graph, c->stream));
+    g_launches.fetch_add((long long)(L - 1) * 5 + 1, std::memory_order_relaxed);
+    CU(cudaMemcpyAsync(c->h_ctl, c->d_ctl, sizeof(DevCtl), cudaMemcpyDeviceToHost, c->stream));
+    CU(cudaMemcpyAsync(c->h_records, c->d_records, sizeof(LgbCuSplitRecord) * (size_t)(L - 1), cudaMemcpyDeviceToHost, c->stream));
+    CU(cudaStreamSynchronize(c->stream));
+    const int n = c->h_ctl->num_splits;
+    NEED(n >= 0 && n <= L - 1, "lgbcu_train_tree: corrupt split count %d", n);
+    std::memcpy(records, c->h_records, sizeof(LgbCuSplitRecord) * (size_t)n);
+    *num_splits = n;
     return 0;
   }
   if (prof && (int)c->ev.size() < 2 * L) {

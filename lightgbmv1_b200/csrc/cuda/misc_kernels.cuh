@@ -84,6 +84,7 @@ __global__ void k_prepare_tree(DevView V, int root_count, int root_identity) {
     none.left_output = none.right_output = 0; none.left_sum_g = none.left_sum_h = 0;
     none.right_sum_g = none.right_sum_h = 0;
     V.best[l] = none;
+    { SplitKey k; k.gain = LGB_MIN_SCORE; k.real_feature = -1; k.pad = 0; V.leaf_key[l] = k; }
     DevLeaf z; z.begin = 0; z.count = 0; z.slot = l; z.depth = 0; z.buf = 0; z.gcount = 0;
     z.sum_g = z.sum_h = z.output = 0; z.tot_g = z.tot_h = 0;
     if (l == 0) { z.count = root_count; z.gcount = groot; }

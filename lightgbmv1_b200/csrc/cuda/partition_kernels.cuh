@@ -192,8 +192,10 @@ __device__ void part_scan_phase(const DevView& V, int mode) {
   if (!skip && gr < V.p.min_data_in_leaf * 2 && gl < V.p.min_data_in_leaf * 2) skip = 1;
   if (skip) {
     V.best[leaf].gain = LGB_MIN_SCORE;
+    V.leaf_key[leaf].gain = LGB_MIN_SCORE;
     DevSplit none; none.gain = LGB_MIN_SCORE; none.feature = -1; none.real_feature = -1;
     V.best[R] = none;
+    { SplitKey k; k.gain = LGB_MIN_SCORE; k.real_feature = -1; k.pad = 0; V.leaf_key[R] = k; }
   }
   c->skip_find = skip;
   if (c->num_leaves >= V.p.num_leaves) c->done = 2;  // tree is full; nothing more to enqueue

@@ -430,6 +430,7 @@ __device__ void find_item(const DevView& V, ScanSmem& S, int f, int sel, int sma
       }
       if (tid == 0) {
         V.feat_best[f] = o;
+        { SplitKey k; k.gain = o.gain; k.real_feature = o.real_feature; k.pad = 0; V.feat_key[f] = k; }
         V.splittable[(size_t)Ls.slot * V.num_features + f] = (int8_t)sp;
       }
     } else {
@@ -474,6 +475,7 @@ __device__ void find_item(const DevView& V, ScanSmem& S, int f, int sel, int sma
       }
       if (tid == 0) {
         V.feat_best[V.num_features + f] = o;
+        { SplitKey k; k.gain = o.gain; k.real_feature = o.real_feature; k.pad = 0; V.feat_key[V.num_features + f] = k; }
         if (used) V.splittable[(size_t)Ll.slot * V.num_features + f] = (int8_t)sp;
       }
     }
@@ -482,64 +484,100 @@ __device__ void find_item(const DevView& V, ScanSmem& S, int f, int sel, int sma
 }
 
 // Reduce the per-feature candidates of the two scanned leaves (SplitInfo::operator>), then pick the next leaf to
-// split (ArgMax over best_split_per_leaf_) and publish the split descriptor.  One warp.
+// split (ArgMax over best_split_per_leaf_) and publish the split descriptor.  One warp.  Everything it compares is
+// read from the compact 16-byte key arrays with independent, coalesced loads (the per-leaf keys are prefetched
+// before the feature reduction), so the step costs ~3 dependent memory round trips instead of a dozen.
+#define CTRL_MAX_LEAF_KEYS 8   /* 32 lanes x 8 = 256 leaves prefetched; more are handled by a second pass */
 __device__ void find_control(const DevView& V, int mode, bool active, int smaller, int larger) {
   DevCtl* c = V.ctl;
   const int lane = threadIdx.x & 31;
+  const int F = V.num_features;
+  const int nl = c->num_leaves;
+  // prefetch the keys of all current leaves (used by the final arg-max)
+  SplitKey lk[CTRL_MAX_LEAF_KEYS];
+#pragma unroll
+  for (int k = 0; k < CTRL_MAX_LEAF_KEYS; ++k) {
+    const int l = lane + 32 * k;
+    lk[k].gain = LGB_MIN_SCORE; lk[k].real_feature = -1; lk[k].pad = 0;
+    if (mode == 0 && l < nl) lk[k] = V.leaf_key[l];
+  }
+  DevSplit rec[2];
+  SplitKey fresh[2];
+  int fresh_leaf[2] = {-1, -1};
   if (active) {
+    int widx[2] = {-1, -1};
+#pragma unroll
     for (int sel = 0; sel < 2; ++sel) {
       const int leaf = sel == 0 ? smaller : larger;
       if (leaf < 0) continue;
       double bg = LGB_MIN_SCORE; int bf = -1, bi = -1;
-      for (int j = lane; j < V.num_features; j += 32) {
-        const DevSplit* s = &V.feat_best[sel * V.num_features + j];
-        const double g = s->gain; const int rf = s->real_feature;
-        if (bi < 0 || split_better(g, rf, bg, bf)) { bg = g; bf = rf; bi = j; }
+      for (int j = lane; j < F; j += 32) {
+        const SplitKey k = V.feat_key[sel * F + j];
+        if (bi < 0 || split_better(k.gain, k.real_feature, bg, bf)) { bg = k.gain; bf = k.real_feature; bi = j; }
       }
       for (int o = 16; o > 0; o >>= 1) {
-        const double g2 = __shfl_down_sync(FULL_MASK, bg, o);
-        const int f2 = __shfl_down_sync(FULL_MASK, bf, o);
-        const int i2 = __shfl_down_sync(FULL_MASK, bi, o);
+        const double g2 = __shfl_xor_sync(FULL_MASK, bg, o);
+        const int f2 = __shfl_xor_sync(FULL_MASK, bf, o);
+        const int i2 = __shfl_xor_sync(FULL_MASK, bi, o);
+        // (gain, feature) is a total order over distinct features, so every lane converges to the same winner
         if (i2 >= 0 && (bi < 0 || split_better(g2, f2, bg, bf))) { bg = g2; bf = f2; bi = i2; }
       }
-      if (lane == 0) {
-        DevSplit r;
-        if (bi >= 0) r = V.feat_best[sel * V.num_features + bi];
-        else { r.gain = LGB_MIN_SCORE; r.feature = -1; r.real_feature = -1; }
-        V.best[leaf] = r;
+      widx[sel] = bi;
+      fresh_leaf[sel] = leaf;
+      fresh[sel].gain = bi >= 0 ? bg : LGB_MIN_SCORE;
+      fresh[sel].real_feature = bi >= 0 ? bf : -1;
+      fresh[sel].pad = 0;
+    }
+    if (lane == 0) {
+#pragma unroll
+      for (int sel = 0; sel < 2; ++sel) {
+        if (fresh_leaf[sel] < 0) continue;
+        if (widx[sel] >= 0) rec[sel] = V.feat_best[sel * F + widx[sel]];
+        else { rec[sel].gain = LGB_MIN_SCORE; rec[sel].feature = -1; rec[sel].real_feature = -1; }
+      }
+#pragma unroll
+      for (int sel = 0; sel < 2; ++sel) {
+        if (fresh_leaf[sel] < 0) continue;
+        V.best[fresh_leaf[sel]] = rec[sel];
+        V.leaf_key[fresh_leaf[sel]] = fresh[sel];
       }
     }
   }
-  __syncwarp();
   if (mode != 0) return;
-  __threadfence_block();
   // ArrayArgs<SplitInfo>::ArgMax(best_split_per_leaf_): first leaf with the best (gain, feature)
-  {
-    const int nl = c->num_leaves;
-    double bg = LGB_MIN_SCORE; int bf = -1, bl = -1;
-    for (int l = lane; l < nl; l += 32) {
-      const double g = V.best[l].gain; const int rf = V.best[l].real_feature;
-      if (bl < 0 || split_better(g, rf, bg, bf)) { bg = g; bf = rf; bl = l; }
+  double bg = LGB_MIN_SCORE; int bf = -1, bl = -1;
+  auto consider = [&](int l, SplitKey k) {
+    if (l == fresh_leaf[0]) k = fresh[0];
+    if (l == fresh_leaf[1]) k = fresh[1];
+    if (bl < 0 || split_better(k.gain, k.real_feature, bg, bf)) { bg = k.gain; bf = k.real_feature; bl = l; }
+  };
+#pragma unroll
+  for (int k = 0; k < CTRL_MAX_LEAF_KEYS; ++k) {
+    const int l = lane + 32 * k;
+    if (l < nl) consider(l, lk[k]);
+  }
+  for (int l = lane + 32 * CTRL_MAX_LEAF_KEYS; l < nl; l += 32) consider(l, V.leaf_key[l]);
+  for (int o = 16; o > 0; o >>= 1) {
+    const double g2 = __shfl_xor_sync(FULL_MASK, bg, o);
+    const int f2 = __shfl_xor_sync(FULL_MASK, bf, o);
+    const int l2 = __shfl_xor_sync(FULL_MASK, bl, o);
+    if (l2 >= 0) {
+      if (bl < 0 || split_better(g2, f2, bg, bf) || (g2 == bg && f2 == bf && l2 < bl)) { bg = g2; bf = f2; bl = l2; }
     }
-    for (int o = 16; o > 0; o >>= 1) {
-      const double g2 = __shfl_down_sync(FULL_MASK, bg, o);
-      const int f2 = __shfl_down_sync(FULL_MASK, bf, o);
-      const int l2 = __shfl_down_sync(FULL_MASK, bl, o);
-      if (l2 >= 0) {
-        if (bl < 0 || split_better(g2, f2, bg, bf) || (g2 == bg && f2 == bf && l2 < bl)) { bg = g2; bf = f2; bl = l2; }
-      }
-    }
-    if (lane == 0) {
-      if (bl < 0 || !(bg > 0.0)) {
-        c->done = 1;  // "No further splits with positive gain"
-      } else {
-        const DevSplit s = V.best[bl];
-        c->split_leaf = bl;
-        c->split_feature = s.feature;
-        c->split_threshold = s.threshold;
-        c->split_default_left = s.default_left;
-        c->split_right_leaf = nl;
-      }
+  }
+  if (lane == 0) {
+    if (bl < 0 || !(bg > 0.0)) {
+      c->done = 1;  // "No further splits with positive gain"
+    } else {
+      DevSplit s;
+      if (bl == fresh_leaf[0]) s = rec[0];
+      else if (bl == fresh_leaf[1]) s = rec[1];
+      else s = V.best[bl];
+      c->split_leaf = bl;
+      c->split_feature = s.feature;
+      c->split_threshold = s.threshold;
+      c->split_default_left = s.default_left;
+      c->split_right_leaf = nl;
     }
   }
 }
