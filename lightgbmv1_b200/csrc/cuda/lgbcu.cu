@@ -116,6 +116,7 @@ struct LgbCuContext {
   // config
   int hist_mode = LGBCU_HIST_AUTO;
   int hist_min_rows = HIST_MIN_ROWS_PER_WARP;
+  bool force_dp_counts = false;  // LGBCU_FORCE_DP_COUNTS=1: single rank, but leaf counts as in data-parallel mode (tests)
   cudaGraphExec_t tree_graph = nullptr; bool use_graph = true;  // the per-tree launch sequence, captured once
   bool persistent_ok = false, use_persistent = false;  // launch-per-phase loop measured faster (profiles/r1_c); LGBCU_PERSISTENT=1 selects k_grow_tree
   int objective = LGBCU_OBJ_NONE; double obj_p[3] = {0, 0, 0};
@@ -133,7 +134,7 @@ struct LgbCuContext {
     V.grad = d_grad; V.hess = d_hess; V.indices[0] = d_indices[0]; V.indices[1] = d_indices[1];
     V.pool = d_pool; V.leaves = d_leaves; V.best = d_best; V.feat_best = d_feat_best; V.feat_key = d_feat_key; V.leaf_key = d_leaf_key; V.ctl = d_ctl;
     V.records = d_records; V.tile_left = d_tile_left; V.part_bits = d_part_bits; V.p = params;
-    V.data_parallel = comm != nullptr ? 1 : 0;
+    V.data_parallel = (comm != nullptr || force_dp_counts) ? 1 : 0;
     return V;
   }
 };
@@ -255,6 +256,7 @@ int lgbcu_create(int device_id, LgbCuContext** out) {
     c->persistent_ok = coop != 0 && per_sm >= 1;
     if (const char* e = std::getenv("LGBCU_PERSISTENT")) c->use_persistent = std::atoi(e) != 0;
     if (const char* e = std::getenv("LGBCU_GRAPH")) c->use_graph = std::atoi(e) != 0;
+    if (const char* e = std::getenv("LGBCU_FORCE_DP_COUNTS")) c->force_dp_counts = std::atoi(e) != 0;
   }
   *out = c;
   return 0;

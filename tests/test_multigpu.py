@@ -1,0 +1,83 @@
+"""tree_learner=data over NCCL: (gpu, needs >= 2 GPUs) the 2-rank model must equal the 1-rank model grown with the
+same bin mappers and the data-parallel count semantics -- exact, because the histogram all-reduce is an integer sum.
+(cpu, gloo, world_size 2) the host-side shard plumbing: shards built against a common reference dataset carry the
+same bin mappers and together hold exactly the bins of the unsharded matrix."""
+import ctypes as C
+import os
+import subprocess
+import sys
+
+import numpy as np
+import pytest
+
+import capi
+import helpers as H
+from lightgbmv1_b200 import _native as N
+
+
+@pytest.mark.gpu
+def test_two_rank_model_equals_one_rank_model(tmp_path):
+    if N.device_count() < 2:
+        pytest.skip("needs 2 GPUs")
+    env = dict(os.environ)
+    one, two = str(tmp_path / "one.txt"), str(tmp_path / "two.txt")
+    script = os.path.join(H.ROOT, "tools", "run_dp.py")
+    env1 = dict(env, LGBCU_FORCE_DP_COUNTS="1")
+    subprocess.check_call([sys.executable, script, "--out", one], env=env1, timeout=600)
+    subprocess.check_call([sys.executable, "-m", "torch.distributed.run", "--nnodes=1", "--nproc-per-node=2",
+                           "--master-addr", "127.0.0.1", "--master-port", "29511", script, "--out", two],
+                          env=env, timeout=900)
+    a, b = open(one).read(), open(two).read()
+    same, n, first = capi.compare_models(a, b, rtol_value=0.0)
+    assert same == n == 5, (same, n, first)
+    assert a.split("parameters:")[0] == b.split("parameters:")[0]
+
+
+def _gloo_worker(rank, world, port, q):
+    import torch.distributed as dist
+    os.environ["MASTER_ADDR"] = "127.0.0.1"; os.environ["MASTER_PORT"] = str(port)
+    dist.init_process_group("gloo", rank=rank, world_size=world)
+    import torch
+    ours = capi.ours()
+    rng = np.random.default_rng(0)
+    n, F = 6000, 7
+    X = rng.standard_normal((n, F)).astype(np.float32)
+    X[:, 3] = np.maximum(0, X[:, 3])
+    ref_ds = ours.dataset_from_mat(X[:2000], "max_bin=63 verbosity=-1")
+    lo, hi = rank * n // world, (rank + 1) * n // world
+    ds = ours.dataset_from_mat(np.ascontiguousarray(X[lo:hi]), "max_bin=63 verbosity=-1", reference=ref_ds)
+    nf = C.c_int(); ours.check(ours.lib.LGBM_B200_DatasetNumInnerFeatures(ds, C.byref(nf)))
+    bins = np.empty((hi - lo, nf.value), dtype=np.int32); real = np.empty(nf.value, dtype=np.int32)
+    ours.check(ours.lib.LGBM_B200_DatasetDumpBins(ds, bins.ctypes.data_as(C.POINTER(C.c_int32)),
+                                                  real.ctypes.data_as(C.POINTER(C.c_int32))))
+    # the rendezvous payload travels like the NCCL id would: rank 0's 128 bytes to everyone
+    uid = torch.arange(128, dtype=torch.uint8) if rank == 0 else torch.zeros(128, dtype=torch.uint8)
+    dist.broadcast(uid, 0)
+    assert uid.tolist() == list(range(128))
+    gathered = [None] * world
+    dist.all_gather_object(gathered, (lo, hi, real.tolist(), int(bins.sum()), bins.tobytes()))
+    if rank == 0:
+        full = ours.dataset_from_mat(X, "max_bin=63 verbosity=-1", reference=ref_ds)
+        fb = np.empty((n, nf.value), dtype=np.int32); fr = np.empty(nf.value, dtype=np.int32)
+        ours.check(ours.lib.LGBM_B200_DatasetDumpBins(full, fb.ctypes.data_as(C.POINTER(C.c_int32)),
+                                                      fr.ctypes.data_as(C.POINTER(C.c_int32))))
+        ok = True
+        for (a, b, r, _, raw) in gathered:
+            ok = ok and r == fr.tolist()
+            ok = ok and np.array_equal(np.frombuffer(raw, dtype=np.int32).reshape(b - a, nf.value), fb[a:b])
+        q.put(ok)
+    dist.barrier()
+    dist.destroy_process_group()
+
+
+def test_row_shards_share_mappers_gloo_world2():
+    import torch.multiprocessing as mp
+    ctx = mp.get_context("spawn")
+    q = ctx.Queue()
+    procs = [ctx.Process(target=_gloo_worker, args=(r, 2, 29533, q)) for r in range(2)]
+    for p in procs:
+        p.start()
+    for p in procs:
+        p.join(timeout=180)
+        assert p.exitcode == 0
+    assert q.get(timeout=5) is True
