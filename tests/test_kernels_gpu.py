@@ -418,3 +418,62 @@ def test_errors_are_reported_not_fatal():
     with pytest.raises(N.LgbCuError):
         L.set_dataset(np.zeros((4, 1), np.uint8), [(300, 0, 0, 0)])   # > 8-bit bins
     L.close()
+
+
+def test_lambdarank_gradients_match_oracle(orc):
+    rng = np.random.default_rng(21)
+    sizes = np.clip(rng.poisson(90, size=400), 1, 700).astype(np.int32)
+    sizes[5] = 1; sizes[17] = 650
+    n = int(sizes.sum())
+    bounds = np.concatenate([[0], np.cumsum(sizes)]).astype(np.int32)
+    label = rng.choice(5, size=n, p=[.52, .32, .13, .02, .01]).astype(np.float32)
+    score = np.round(rng.standard_normal(n) * 2, 2)   # ties exercise the stable sort
+    weight = (rng.random(n) + 0.5).astype(np.float32)
+    gains = np.array([0.0] + [float((1 << i) - 1) for i in range(1, 31)])
+    for w in (None, weight):
+        for norm in (1, 0):
+            L = N.CudaLearner()
+            L.set_dataset(np.zeros((n, 1), np.uint8), [(4, 0, 0, 0)])
+            L.set_label(label); L.set_weight(w); L.set_query(bounds)
+            L.set_score(score)
+            L.set_objective(N.OBJ_LAMBDARANK, 1.0, 20, norm)
+            L.get_gradients()
+            g, h = L.copy_gradients()
+            wg = np.empty(n, np.float32); wh = np.empty(n, np.float32)
+            orc.orc_grad_lambdarank(C.c_int(len(sizes)), H.fptr(bounds, C.c_int32), H.fptr(score, C.c_double),
+                                    H.fptr(label, C.c_float), None if w is None else H.fptr(w, C.c_float), C.c_double(1.0),
+                                    C.c_int(20), C.c_int(norm), H.fptr(gains, C.c_double), C.c_int(len(gains)),
+                                    H.fptr(wg, C.c_float), H.fptr(wh, C.c_float))
+            # per-document float accumulation is replayed in the reference's order: bit-exact except that the
+            # normalisation factor sums the pair lambdas in a different (block-reduction) order: <= 1 float ulp
+            assert np.max(np.abs(g - wg) / np.maximum(np.abs(wg), 1e-30)) <= 2.5e-7
+            assert np.max(np.abs(h - wh) / np.maximum(np.abs(wh), 1e-30)) <= 2.5e-7
+            if norm == 0:
+                assert np.array_equal(g, wg) and np.array_equal(h, wh)
+            L.close()
+
+
+def test_wide_feature_matrix_like_epsilon(orc):
+    # config #3 shape in miniature: 2000 features (125 feature tiles), every feature 255 bins
+    n, F = 6000, 2000
+    rng = np.random.default_rng(31)
+    metas = [(255, 127, 127, 0)] * F
+    bins = rng.integers(0, 256, size=(n, F), dtype=np.int64)
+    bins = np.where(bins == 128, 0, bins).astype(np.uint8)  # stored 0 = most frequent bin, 128 would be its own slot
+    g = rng.standard_normal(n).astype(np.float32)
+    g += (0.7 * np.sign(bins[:, 1234].astype(np.float32) - 100)).astype(np.float32)
+    h = (rng.random(n) * 0.25 + 0.01).astype(np.float32)
+    params = N.make_tree_params(num_leaves=15, min_data_in_leaf=20)
+    L = N.CudaLearner()
+    L.set_dataset(bins, metas); L.set_tree_params(params); L.set_gradients(g, h)
+    L.begin_tree()
+    L.hist_build(0)
+    got = L.hist_read(0)
+    want = _oracle_hist(orc, bins, metas, None, g, h)
+    assert _compare_hist(metas, got, want, g, h) <= H.HIST_RTOL
+    L.begin_tree()
+    recs = L.train_tree()
+    want_recs, leaf_of_row = _orc_train(orc, bins, metas, params, g, h)
+    assert len(want_recs) >= 3 and recs[0].feature == 1234
+    _check_tree(L, recs, want_recs, leaf_of_row, n)
+    L.close()
