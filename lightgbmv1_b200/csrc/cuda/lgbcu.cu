@@ -125,6 +125,7 @@ struct LgbCuContext {
   bool profile = false;
   std::vector<cudaEvent_t> ev;
   double prof_hist_ms = 0; long long prof_hist_calls = 0; double prof_hist_bytes = 0;
+  double loop_phase_ms[8] = {0, 0, 0, 0, 0, 0, 0, 0}; bool loop_phase_valid = false;
 
   DevView view() const {
     DevView V;
@@ -802,21 +803,28 @@ int lgbcu_train_tree(LgbCuContext* c, LgbCuSplitRecord* records, int32_t* num_sp
     *num_splits = n;
     return 0;
   }
-  if (prof && (int)c->ev.size() < 2 * L) {
+  // launch-per-phase loop (profiling, data-parallel, or graph disabled).  In profile mode every launch is bracketed
+  // by events so that per-phase device time (warm caches, real dependencies) can be reported.
+  const int EV = 6;  // events per split: before hist, after hist, after find, after flags, after scan, after scatter
+  if (prof && (int)c->ev.size() < EV * L) {
     const size_t old = c->ev.size();
-    c->ev.resize(2 * L);
+    c->ev.resize(EV * L);
     for (size_t i = old; i < c->ev.size(); ++i) CU(cudaEventCreate(&c->ev[i]));
   }
   for (int s = 0; s < L - 1; ++s) {
-    if (prof) CU(cudaEventRecord(c->ev[2 * s], c->stream));
+    if (prof) CU(cudaEventRecord(c->ev[EV * s], c->stream));
     if (launch_hist(c, -1)) return -1;
-    if (prof) CU(cudaEventRecord(c->ev[2 * s + 1], c->stream));
     if (comm_reduce_hist(c, s)) return -1;
     if (s == 0) LAUNCH(k_root_sums, 1, 32, 0, c->stream, V);
+    if (prof) CU(cudaEventRecord(c->ev[EV * s + 1], c->stream));
     LAUNCH(k_find_split, dim3(c->F, 2), FS_THREADS, 0, c->stream, V, 0, -1);
+    if (prof) CU(cudaEventRecord(c->ev[EV * s + 2], c->stream));
     LAUNCH(k_part_flags, part_grid, PART_THREADS, 0, c->stream, V);
+    if (prof) CU(cudaEventRecord(c->ev[EV * s + 3], c->stream));
     LAUNCH(k_part_scan, 1, 1024, 0, c->stream, V, 0);
+    if (prof) CU(cudaEventRecord(c->ev[EV * s + 4], c->stream));
     LAUNCH(k_part_scatter, part_grid, PART_THREADS, 0, c->stream, V, 0);
+    if (prof) CU(cudaEventRecord(c->ev[EV * s + 5], c->stream));
   }
   CU(cudaGetLastError());
   CU(cudaMemcpyAsync(c->h_ctl, c->d_ctl, sizeof(DevCtl), cudaMemcpyDeviceToHost, c->stream));
@@ -827,10 +835,16 @@ int lgbcu_train_tree(LgbCuContext* c, LgbCuSplitRecord* records, int32_t* num_sp
   std::memcpy(records, c->h_records, sizeof(LgbCuSplitRecord) * (size_t)n);
   *num_splits = n;
   if (prof) {
+    for (int i = 0; i < 8; ++i) c->loop_phase_ms[i] = 0;
+    const int slot[5] = {0, 2, 4, 5, 6};  // hist, find(+control), flags, scan, scatter
     for (int s = 0; s < L - 1; ++s) {
-      float ms = 0; CU(cudaEventElapsedTime(&ms, c->ev[2 * s], c->ev[2 * s + 1]));
-      c->prof_hist_ms += ms;
+      for (int k = 0; k < 5; ++k) {
+        float ms = 0; CU(cudaEventElapsedTime(&ms, c->ev[EV * s + k], c->ev[EV * s + k + 1]));
+        c->loop_phase_ms[slot[k]] += ms;
+        if (k == 0) c->prof_hist_ms += ms;
+      }
     }
+    c->loop_phase_valid = true;
   }
   return 0;
 }
@@ -840,7 +854,7 @@ int lgbcu_profile_phases(LgbCuContext* c, double* ms8) {
   CU(cudaSetDevice(c->device));
   CU(cudaMemcpyAsync(c->h_ctl, c->d_ctl, sizeof(DevCtl), cudaMemcpyDeviceToHost, c->stream));
   CU(cudaStreamSynchronize(c->stream));
-  for (int i = 0; i < 8; ++i) ms8[i] = (double)c->h_ctl->prof_phase_ns[i] * 1e-6;
+  for (int i = 0; i < 8; ++i) ms8[i] = c->loop_phase_valid ? c->loop_phase_ms[i] : (double)c->h_ctl->prof_phase_ns[i] * 1e-6;
   return 0;
 }
 
