@@ -83,6 +83,7 @@ __device__ void hist_private_path(const DevView& V, const DevLeaf& L, bool ident
   const bool worker = warp < HIST_WARPS_PER_BLOCK;
   const int wslot = worker ? warp : 0;
   i64* H = reinterpret_cast<i64*>(smem + (size_t)wslot * HIST_SUB_BYTES);
+  i64* Hl = H + lane;  // this lane's column
   const i64* H0 = reinterpret_cast<const i64*>(smem);
   const i64* H1 = reinterpret_cast<const i64*>(smem + (size_t)HIST_SUB_BYTES);
   const i64* H2 = reinterpret_cast<const i64*>(smem + (size_t)2 * HIST_SUB_BYTES);
@@ -148,24 +149,25 @@ __device__ void hist_private_path(const DevView& V, const DevLeaf& L, bool ident
         int n = r1 - base; if (n > 32) n = 32;
         if (n == 32) {
           // 4 rows in flight: their 4 read-modify-writes are independent unless two rows of this lane's feature
-          // share a bin.  Duplicates are folded forward (the last row of a bin carries the sum, earlier ones add
-          // 0), all 4 loads are issued before the 4 stores, and stores stay in row order: the sequential result.
+          // share a bin; then the later row's (stale) loaded value is patched with the earlier rows' addends.
+          // Stores stay in row order, so the result is the sequential one.
 #pragma unroll
           for (int j0 = 0; j0 < 32; j0 += 4) {
             const unsigned c0 = sb8[(j0 + 0) * 16 + fl], c1 = sb8[(j0 + 1) * 16 + fl];
             const unsigned c2 = sb8[(j0 + 2) * 16 + fl], c3 = sb8[(j0 + 3) * 16 + fl];
-            i64 v0 = sv64[(j0 + 0) * 2 + ch], v1 = sv64[(j0 + 1) * 2 + ch];
-            i64 v2 = sv64[(j0 + 2) * 2 + ch], v3 = sv64[(j0 + 3) * 2 + ch];
-            if (c1 == c0) { v1 += v0; v0 = 0; }
-            if (c2 == c0) { v2 += v0; v0 = 0; }
-            if (c2 == c1) { v2 += v1; v1 = 0; }
-            if (c3 == c0) { v3 += v0; v0 = 0; }
-            if (c3 == c1) { v3 += v1; v1 = 0; }
-            if (c3 == c2) { v3 += v2; v2 = 0; }
-            i64* p0 = H + (c0 * 32 + lane); i64* p1 = H + (c1 * 32 + lane);
-            i64* p2 = H + (c2 * 32 + lane); i64* p3 = H + (c3 * 32 + lane);
-            const i64 a0 = *p0, a1 = *p1, a2 = *p2, a3 = *p3;
-            *p0 = a0 + v0; *p1 = a1 + v1; *p2 = a2 + v2; *p3 = a3 + v3;
+            const i64 v0 = sv64[(j0 + 0) * 2 + ch], v1 = sv64[(j0 + 1) * 2 + ch];
+            const i64 v2 = sv64[(j0 + 2) * 2 + ch], v3 = sv64[(j0 + 3) * 2 + ch];
+            i64* p0 = Hl + c0 * 32; i64* p1 = Hl + c1 * 32;
+            i64* p2 = Hl + c2 * 32; i64* p3 = Hl + c3 * 32;
+            i64 a0 = *p0, a1 = *p1, a2 = *p2, a3 = *p3;   // all four loads before any store
+            // a later row that shares a bin with an earlier one loaded a stale value: add what the earlier rows add
+            if (c1 == c0) a1 += v0;
+            if (c2 == c0) a2 += v0;
+            if (c2 == c1) a2 += v1;
+            if (c3 == c0) a3 += v0;
+            if (c3 == c1) a3 += v1;
+            if (c3 == c2) a3 += v2;
+            *p0 = a0 + v0; *p1 = a1 + v1; *p2 = a2 + v2; *p3 = a3 + v3;  // row order: the last store of a bin wins
           }
         } else {
           for (int j = 0; j < n; ++j) {
