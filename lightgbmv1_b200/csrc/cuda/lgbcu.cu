@@ -294,6 +294,7 @@ int lgbcu_synchronize(LgbCuContext* c) {
 static int setup_dataset_common(LgbCuContext* c, int32_t num_data, int32_t num_features, const LgbCuFeatureMeta* meta) {
   NEED(c, "lgbcu: NULL context");
   NEED(num_data > 0 && num_features > 0 && meta, "lgbcu_set_dataset: empty dataset");
+  NEED(num_features < (1 << KEY_FEAT_BITS), "lgbcu_set_dataset: %d features exceed the supported %d", num_features, (1 << KEY_FEAT_BITS) - 1);
   CU(cudaSetDevice(c->device));
   c->N = num_data; c->F = num_features;
   c->stride = (num_features + 15) & ~15;
@@ -857,6 +858,16 @@ int lgbcu_profile_phases(LgbCuContext* c, double* ms8) {
   for (int i = 0; i < 8; ++i) ms8[i] = c->loop_phase_valid ? c->loop_phase_ms[i] : (double)c->h_ctl->prof_phase_ns[i] * 1e-6;
   return 0;
 }
+
+#ifdef LGBCU_STAGE_TIMERS
+extern "C" int lgbcu_debug_stages(unsigned long long* out16, int reset) {
+  unsigned long long z[16] = {0};
+  cudaDeviceSynchronize();
+  cudaMemcpyFromSymbol(out16, g_stage_cycles, sizeof(z));
+  if (reset) cudaMemcpyToSymbol(g_stage_cycles, z, sizeof(z));
+  return 0;
+}
+#endif
 
 int lgbcu_profile_enable(LgbCuContext* c, int on) {
   NEED(c, "lgbcu: NULL context");

@@ -15,6 +15,16 @@
 #include "dev_types.cuh"
 
 #define FULL_MASK 0xffffffffu
+#ifdef LGBCU_STAGE_TIMERS
+__device__ unsigned long long g_stage_cycles[16];
+__device__ long long g_stage_prev;
+#define STAGE(i) do { if (blockIdx.x == 0 && blockIdx.y == 1 && threadIdx.x == 0) { long long t_ = clock64(); \
+    g_stage_cycles[i] += (unsigned long long)(t_ - g_stage_prev); g_stage_prev = t_; } } while (0)
+#define STAGE_BEGIN() do { if (blockIdx.x == 0 && blockIdx.y == 1 && threadIdx.x == 0) g_stage_prev = clock64(); } while (0)
+#else
+#define STAGE(i) do {} while (0)
+#define STAGE_BEGIN() do {} while (0)
+#endif
 #define BINS_PER_LANE 8
 
 __device__ __forceinline__ int sign_of(double x) { return (x > 0.0) - (x < 0.0); }  // Common::Sign
@@ -62,14 +72,12 @@ __device__ __forceinline__ Cand cand_better(const Cand& a, const Cand& b, bool p
   return take_b ? b : a;
 }
 
+// Only (gain, t) travel through the reduction; the winner's sums are looked up again afterwards.
 __device__ __forceinline__ Cand warp_best_cand(Cand c, bool prefer_high) {
   for (int o = 16; o > 0; o >>= 1) {
-    Cand x;
+    Cand x = c;
     x.gain = __shfl_xor_sync(FULL_MASK, c.gain, o);
-    x.left_g = __shfl_xor_sync(FULL_MASK, c.left_g, o);
-    x.left_h = __shfl_xor_sync(FULL_MASK, c.left_h, o);
     x.t = __shfl_xor_sync(FULL_MASK, c.t, o);
-    x.left_count = __shfl_xor_sync(FULL_MASK, c.left_count, o);
     c = cand_better(c, x, prefer_high);
   }
   return c;
@@ -145,6 +153,12 @@ __device__ __forceinline__ void chain_cnt(const int* __restrict__ c, int* out, i
     }
   }
   *acc_io = acc;
+}
+
+// SplitKey::pad = inner feature | threshold << 20 | default_left << 29 (bins are 8-bit, so a threshold fits 9 bits)
+#define KEY_FEAT_BITS 20
+__device__ __forceinline__ int key_pack(int feature, int threshold, int default_left) {
+  return feature | (threshold << KEY_FEAT_BITS) | (default_left << (KEY_FEAT_BITS + 9));
 }
 
 #define FS_THREADS 256
@@ -238,6 +252,7 @@ __device__ void scan_feature_block(ScanSmem& S, int nt, const DevFeat& F, double
     if (tid == 0) S.base_g = base_g;
   }
   __syncthreads();
+  STAGE(2);
   // ---- four sequential chains on four warps
   if (tid == 0) {  // reverse hessian chain (starts from kEpsilon: order matters)
     double ah = LGB_EPS;
@@ -263,6 +278,7 @@ __device__ void scan_feature_block(ScanSmem& S, int nt, const DevFeat& F, double
     chain_cnt<1>(S.cnt, S.LC, 0, t_end, skip_t, 1, &lc);
   }
   __syncthreads();
+  STAGE(3);
   // ---- one threshold per thread
   int splittable = 0;
   Cand rb; rb.gain = LGB_MIN_SCORE; rb.t = -1000; rb.left_g = 0; rb.left_h = 0; rb.left_count = 0;
@@ -323,6 +339,14 @@ __device__ void scan_feature_block(ScanSmem& S, int nt, const DevFeat& F, double
   for (int w = 0; w < FS_WARPS; ++w) {
     any_split |= S.wsplit[w];
     if (w) { rb = cand_better(rb, S.wbest[0][w], true); fb = cand_better(fb, S.wbest[1][w], false); }
+  }
+  // the winners' sums, formed exactly as the evaluating thread formed them
+  if (rb.gain > LGB_MIN_SCORE) {
+    rb.left_count = num_data - S.RC[rb.t]; rb.left_h = sum_h - S.RH[rb.t]; rb.left_g = sum_g - S.RG[rb.t];
+  }
+  if (two_way && fb.gain > LGB_MIN_SCORE) {
+    if (fb.t >= 0) { fb.left_g = S.LG[fb.t]; fb.left_h = S.LH[fb.t]; fb.left_count = S.LC[fb.t]; }
+    else { fb.left_g = S.base_g; fb.left_h = S.base_h; fb.left_count = S.base_c; }
   }
   DevSplit o;
   o.gain = LGB_MIN_SCORE; o.feature = -1; o.real_feature = -1; o.threshold = 0; o.default_left = 1;
@@ -430,7 +454,7 @@ __device__ void find_item(const DevView& V, ScanSmem& S, int f, int sel, int sma
       }
       if (tid == 0) {
         V.feat_best[f] = o;
-        { SplitKey k; k.gain = o.gain; k.real_feature = o.real_feature; k.pad = 0; V.feat_key[f] = k; }
+        { SplitKey k; k.gain = o.gain; k.real_feature = o.real_feature; k.pad = o.feature >= 0 ? key_pack(o.feature, o.threshold, o.default_left) : 0; V.feat_key[f] = k; }
         V.splittable[(size_t)Ls.slot * V.num_features + f] = (int8_t)sp;
       }
     } else {
@@ -470,12 +494,13 @@ __device__ void find_item(const DevView& V, ScanSmem& S, int f, int sel, int sma
         }
         S.gi[tid] = e.g;
         __syncthreads();
+        STAGE(1);
         scan_feature_block(S, nt, F, Ll.sum_g, Ll.sum_h, Ll.gcount, parent_output_of(Ll, larger, V.p), V.p, inv_g, &o, &sp);
         o.feature = f; o.real_feature = F.real_index;
       }
       if (tid == 0) {
         V.feat_best[V.num_features + f] = o;
-        { SplitKey k; k.gain = o.gain; k.real_feature = o.real_feature; k.pad = 0; V.feat_key[V.num_features + f] = k; }
+        { SplitKey k; k.gain = o.gain; k.real_feature = o.real_feature; k.pad = o.feature >= 0 ? key_pack(o.feature, o.threshold, o.default_left) : 0; V.feat_key[V.num_features + f] = k; }
         if (used) V.splittable[(size_t)Ll.slot * V.num_features + f] = (int8_t)sp;
       }
     }
@@ -486,8 +511,11 @@ __device__ void find_item(const DevView& V, ScanSmem& S, int f, int sel, int sma
 // Reduce the per-feature candidates of the two scanned leaves (SplitInfo::operator>), then pick the next leaf to
 // split (ArgMax over best_split_per_leaf_) and publish the split descriptor.  One warp.  Everything it compares is
 // read from the compact 16-byte key arrays with independent, coalesced loads (the per-leaf keys are prefetched
-// before the feature reduction), so the step costs ~3 dependent memory round trips instead of a dozen.
+// before the feature reduction).  A key also carries (inner feature, threshold, default_left) packed in `pad`, so the
+// descriptor of the winning split is known without fetching its 80-byte record; the records of the two scanned
+// leaves are copied feat_best -> best word-parallel by lanes 0..19, off the descriptor's critical path.
 #define CTRL_MAX_LEAF_KEYS 8   /* 32 lanes x 8 = 256 leaves prefetched; more are handled by a second pass */
+#define DEVSPLIT_WORDS ((int)(sizeof(DevSplit) / 4))
 __device__ void find_control(const DevView& V, int mode, bool active, int smaller, int larger) {
   DevCtl* c = V.ctl;
   const int lane = threadIdx.x & 31;
@@ -501,55 +529,68 @@ __device__ void find_control(const DevView& V, int mode, bool active, int smalle
     lk[k].gain = LGB_MIN_SCORE; lk[k].real_feature = -1; lk[k].pad = 0;
     if (mode == 0 && l < nl) lk[k] = V.leaf_key[l];
   }
-  DevSplit rec[2];
   SplitKey fresh[2];
   int fresh_leaf[2] = {-1, -1};
   if (active) {
     int widx[2] = {-1, -1};
+    SplitKey fk[2];
+#pragma unroll
+    for (int sel = 0; sel < 2; ++sel) {  // both key loads are issued before either reduction
+      fk[sel].gain = LGB_MIN_SCORE; fk[sel].real_feature = -1; fk[sel].pad = 0;
+      const int leaf = sel == 0 ? smaller : larger;
+      if (leaf >= 0 && lane < F) fk[sel] = V.feat_key[sel * F + lane];
+    }
 #pragma unroll
     for (int sel = 0; sel < 2; ++sel) {
       const int leaf = sel == 0 ? smaller : larger;
       if (leaf < 0) continue;
-      double bg = LGB_MIN_SCORE; int bf = -1, bi = -1;
-      for (int j = lane; j < F; j += 32) {
+      double bg = LGB_MIN_SCORE; int bf = -1, bi = -1, bp = 0;
+      if (lane < F) { bg = fk[sel].gain; bf = fk[sel].real_feature; bp = fk[sel].pad; bi = lane; }
+      for (int j = lane + 32; j < F; j += 32) {
         const SplitKey k = V.feat_key[sel * F + j];
-        if (bi < 0 || split_better(k.gain, k.real_feature, bg, bf)) { bg = k.gain; bf = k.real_feature; bi = j; }
+        if (split_better(k.gain, k.real_feature, bg, bf)) { bg = k.gain; bf = k.real_feature; bp = k.pad; bi = j; }
       }
       for (int o = 16; o > 0; o >>= 1) {
         const double g2 = __shfl_xor_sync(FULL_MASK, bg, o);
         const int f2 = __shfl_xor_sync(FULL_MASK, bf, o);
         const int i2 = __shfl_xor_sync(FULL_MASK, bi, o);
+        const int p2 = __shfl_xor_sync(FULL_MASK, bp, o);
         // (gain, feature) is a total order over distinct features, so every lane converges to the same winner
-        if (i2 >= 0 && (bi < 0 || split_better(g2, f2, bg, bf))) { bg = g2; bf = f2; bi = i2; }
+        if (i2 >= 0 && (bi < 0 || split_better(g2, f2, bg, bf))) { bg = g2; bf = f2; bi = i2; bp = p2; }
       }
       widx[sel] = bi;
       fresh_leaf[sel] = leaf;
       fresh[sel].gain = bi >= 0 ? bg : LGB_MIN_SCORE;
       fresh[sel].real_feature = bi >= 0 ? bf : -1;
-      fresh[sel].pad = 0;
+      fresh[sel].pad = bi >= 0 ? bp : 0;
     }
-    if (lane == 0) {
+    // best_split_per_leaf_[leaf] = winner: 20 lanes move one 32-bit word each, both loads before both stores
+    {
+      int w[2] = {0, 0};
+#pragma unroll
+      for (int sel = 0; sel < 2; ++sel)
+        if (fresh_leaf[sel] >= 0 && widx[sel] >= 0 && lane < DEVSPLIT_WORDS)
+          w[sel] = reinterpret_cast<const int*>(V.feat_best + (sel * F + widx[sel]))[lane];
 #pragma unroll
       for (int sel = 0; sel < 2; ++sel) {
         if (fresh_leaf[sel] < 0) continue;
-        if (widx[sel] >= 0) rec[sel] = V.feat_best[sel * F + widx[sel]];
-        else { rec[sel].gain = LGB_MIN_SCORE; rec[sel].feature = -1; rec[sel].real_feature = -1; }
-      }
-#pragma unroll
-      for (int sel = 0; sel < 2; ++sel) {
-        if (fresh_leaf[sel] < 0) continue;
-        V.best[fresh_leaf[sel]] = rec[sel];
-        V.leaf_key[fresh_leaf[sel]] = fresh[sel];
+        if (widx[sel] >= 0) {
+          if (lane < DEVSPLIT_WORDS) reinterpret_cast<int*>(V.best + fresh_leaf[sel])[lane] = w[sel];
+        } else if (lane == 0) {
+          DevSplit* r = V.best + fresh_leaf[sel];
+          r->gain = LGB_MIN_SCORE; r->feature = -1; r->real_feature = -1;
+        }
+        if (lane == 0) V.leaf_key[fresh_leaf[sel]] = fresh[sel];
       }
     }
   }
   if (mode != 0) return;
   // ArrayArgs<SplitInfo>::ArgMax(best_split_per_leaf_): first leaf with the best (gain, feature)
-  double bg = LGB_MIN_SCORE; int bf = -1, bl = -1;
+  double bg = LGB_MIN_SCORE; int bf = -1, bl = -1, bp = 0;
   auto consider = [&](int l, SplitKey k) {
     if (l == fresh_leaf[0]) k = fresh[0];
     if (l == fresh_leaf[1]) k = fresh[1];
-    if (bl < 0 || split_better(k.gain, k.real_feature, bg, bf)) { bg = k.gain; bf = k.real_feature; bl = l; }
+    if (bl < 0 || split_better(k.gain, k.real_feature, bg, bf)) { bg = k.gain; bf = k.real_feature; bl = l; bp = k.pad; }
   };
 #pragma unroll
   for (int k = 0; k < CTRL_MAX_LEAF_KEYS; ++k) {
@@ -561,22 +602,19 @@ __device__ void find_control(const DevView& V, int mode, bool active, int smalle
     const double g2 = __shfl_xor_sync(FULL_MASK, bg, o);
     const int f2 = __shfl_xor_sync(FULL_MASK, bf, o);
     const int l2 = __shfl_xor_sync(FULL_MASK, bl, o);
+    const int p2 = __shfl_xor_sync(FULL_MASK, bp, o);
     if (l2 >= 0) {
-      if (bl < 0 || split_better(g2, f2, bg, bf) || (g2 == bg && f2 == bf && l2 < bl)) { bg = g2; bf = f2; bl = l2; }
+      if (bl < 0 || split_better(g2, f2, bg, bf) || (g2 == bg && f2 == bf && l2 < bl)) { bg = g2; bf = f2; bl = l2; bp = p2; }
     }
   }
   if (lane == 0) {
     if (bl < 0 || !(bg > 0.0)) {
       c->done = 1;  // "No further splits with positive gain"
     } else {
-      DevSplit s;
-      if (bl == fresh_leaf[0]) s = rec[0];
-      else if (bl == fresh_leaf[1]) s = rec[1];
-      else s = V.best[bl];
       c->split_leaf = bl;
-      c->split_feature = s.feature;
-      c->split_threshold = s.threshold;
-      c->split_default_left = s.default_left;
+      c->split_feature = bp & ((1 << KEY_FEAT_BITS) - 1);
+      c->split_threshold = (bp >> KEY_FEAT_BITS) & 511;
+      c->split_default_left = (bp >> (KEY_FEAT_BITS + 9)) & 1;
       c->split_right_leaf = nl;
     }
   }
@@ -591,10 +629,13 @@ __global__ void __launch_bounds__(FS_THREADS) k_find_split(DevView V, int mode, 
   __shared__ int s_last;
   DevCtl* c = V.ctl;
   if (mode == 0 && c->done) return;
+  STAGE_BEGIN();
   const bool active = (mode == 1) || !c->skip_find;
   const int smaller = (mode == 1) ? leaf_arg : c->smaller;
   const int larger = (mode == 1) ? -1 : c->larger;
+  STAGE(0);
   if (active) find_item(V, S, blockIdx.x, blockIdx.y, smaller, larger);
+  STAGE(4);
   __threadfence();
   __syncthreads();
   if (threadIdx.x == 0) {
@@ -602,6 +643,12 @@ __global__ void __launch_bounds__(FS_THREADS) k_find_split(DevView V, int mode, 
     s_last = (ticket == gridDim.x * gridDim.y - 1);
   }
   __syncthreads();
+  STAGE(5);
+#ifdef LGBCU_STAGE_TIMERS
+  long long tc0 = clock64();
+  if (s_last && threadIdx.x < 32) { if (threadIdx.x == 0) c->feat_done = 0; find_control(V, mode, active, smaller, larger);
+    if (threadIdx.x == 0) g_stage_cycles[6] += (unsigned long long)(clock64() - tc0); g_stage_cycles[7] += 1; return; }
+#endif
   if (!s_last) return;
   __threadfence();
   if (threadIdx.x >= 32) return;
