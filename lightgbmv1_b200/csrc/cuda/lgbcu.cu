@@ -778,6 +778,7 @@ int lgbcu_train_tree(LgbCuContext* c, LgbCuSplitRecord* records, int32_t* num_sp
     if (!c->tree_graph) {
       cudaGraph_t g = nullptr;
       CU(cudaStreamBeginCapture(c->stream, cudaStreamCaptureModeThreadLocal));
+      const long long before = g_launches.load(std::memory_order_relaxed);  // captured launches are not executions
       bool ok = true;
       for (int s = 0; s < L - 1 && ok; ++s) {
         ok = launch_hist(c, -1) == 0;
@@ -788,6 +789,7 @@ int lgbcu_train_tree(LgbCuContext* c, LgbCuSplitRecord* records, int32_t* num_sp
         LAUNCH(k_part_scatter, part_grid, PART_THREADS, 0, c->stream, V, 0);
       }
       cudaError_t ce = cudaStreamEndCapture(c->stream, &g);
+      g_launches.fetch_add(before - g_launches.load(std::memory_order_relaxed), std::memory_order_relaxed);
       if (!ok || ce != cudaSuccess || !g) { if (g) cudaGraphDestroy(g); return fail("lgbcu_train_tree: graph capture failed (%s)", cudaGetErrorString(ce)); }
       ce = cudaGraphInstantiate(&c->tree_graph, g, 0);
       cudaGraphDestroy(g);
