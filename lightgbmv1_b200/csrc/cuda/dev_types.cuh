@@ -71,9 +71,10 @@ struct DevCtl {
   int kg, kh;        // fixed-point exponents
   double scale_g, scale_h, inv_g, inv_h;
   unsigned feat_done;  // "last block done" counter of k_find_split
-  unsigned pad0;
+  unsigned bar_arrive;  // inter-block barrier of k_partition (self-resetting)
   long long global_root;  // root rows over all ranks   } adjacent: one 2 x int64 sum all-reduce
   long long global_rows;  // dataset rows over all ranks }
+  unsigned bar_depart, pad1;
   unsigned long long prof_hist_rows, prof_hist_rows_indexed, prof_hist_calls, prof_hist_ns;
   unsigned long long prof_phase_ns[8];  // persistent kernel: hist, root, find, control, flags, scan, scatter, (spare)
 };
@@ -108,5 +109,27 @@ struct DevView {
   unsigned* part_bits;       // partition scratch: 1 bit per row (1 = goes left)
   DevParams p;
 };
+
+#ifdef LGBCU_STAGE_TIMERS
+__device__ unsigned long long g_stamps[3 * 4096];
+__device__ __forceinline__ void stamp(const DevCtl* c, int k) {
+  if (blockIdx.x == 0 && blockIdx.y == 0 && threadIdx.x == 0 && c->num_splits < 4096) {
+    unsigned long long t; asm volatile("mov.u64 %0, %globaltimer;" : "=l"(t));
+    g_stamps[3 * c->num_splits + k] = t;
+  }
+}
+__device__ unsigned long long g_ends[3 * 4096];
+__device__ __forceinline__ void stamp_end(int split, int k) {  // every block: latest block exit
+  if (threadIdx.x == 0 && split < 4096) {
+    unsigned long long t; asm volatile("mov.u64 %0, %globaltimer;" : "=l"(t));
+    atomicMax(&g_ends[3 * split + k], t);
+  }
+}
+#define STAMP(c, k) stamp(c, k)
+#define STAMP_END(split, k) stamp_end(split, k)
+#else
+#define STAMP(c, k) do {} while (0)
+#define STAMP_END(split, k) do {} while (0)
+#endif
 
 __device__ __forceinline__ int round_int(double x) { return (int)(x + 0.5f); }  // Common::RoundInt

@@ -214,6 +214,11 @@ __device__ void hist_phase(const DevView& V, int leaf, int mode, int min_rows, i
 __global__ void __launch_bounds__(HIST_THREADS, 1) k_hist(DevView V, int leaf_arg, int mode, int min_rows) {
   extern __shared__ __align__(16) unsigned char hist_smem[];
   int leaf;
+  STAMP(V.ctl, 0);
   if (!hist_target(V, leaf_arg, &leaf)) return;
+#ifdef LGBCU_STAGE_TIMERS
+  const int split_ = V.ctl->num_splits;
+#endif
   hist_phase(V, leaf, mode, min_rows, blockIdx.x, gridDim.x, hist_smem);
+  STAMP_END(split_, 0);
 }

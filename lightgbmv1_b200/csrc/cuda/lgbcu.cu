@@ -184,6 +184,24 @@ int launch_hist(LgbCuContext* c, int leaf_arg) {
   return 0;
 }
 
+// The fused partition spins on an inter-block barrier, so it is launched cooperatively (the runtime then guarantees
+// that the whole grid is resident).  grid = blocks that own tiles (at most 4 per SM) + 1 control block.
+int launch_partition(LgbCuContext* c, long long rows, int mode) {
+  const DevView V = c->view();
+  cudaLaunchConfig_t cfg = {};
+  cfg.gridDim = dim3((unsigned)grid_for(c, rows, PART_TILE, 4) + 1u);
+  cfg.blockDim = dim3(PART_THREADS);
+  cfg.dynamicSmemBytes = 0;
+  cfg.stream = c->stream;
+  cudaLaunchAttribute at[1];
+  at[0].id = cudaLaunchAttributeCooperative;
+  at[0].val.cooperative = 1;
+  cfg.attrs = at; cfg.numAttrs = 1;
+  CU(cudaLaunchKernelEx(&cfg, k_partition, V, mode));
+  g_launches.fetch_add(1, std::memory_order_relaxed);
+  return 0;
+}
+
 // max|g|, max|h| must be the same on every rank: the fixed-point scale is part of the wire format.
 int comm_allreduce_tree_setup(LgbCuContext* c) {
   if (!c->comm) return 0;
@@ -698,9 +716,7 @@ int lgbcu_partition(LgbCuContext* c, int32_t leaf, int32_t inner_feature, int32_
   CU(cudaSetDevice(c->device));
   const DevView V = c->view();
   LAUNCH(k_set_split, 1, 1, 0, c->stream, V, leaf, inner_feature, threshold, default_left, right_leaf);
-  LAUNCH(k_part_flags, grid_for(c, c->N, PART_TILE), PART_THREADS, 0, c->stream, V);
-  LAUNCH(k_part_scan, 1, 1024, 0, c->stream, V, 1);
-  LAUNCH(k_part_scatter, grid_for(c, c->N, PART_TILE), PART_THREADS, 0, c->stream, V, 0);
+  if (launch_partition(c, c->N, 1)) return -1;
   CU(cudaGetLastError());
   CU(cudaMemcpyAsync(c->h_ctl, c->d_ctl, sizeof(DevCtl), cudaMemcpyDeviceToHost, c->stream));
   CU(cudaStreamSynchronize(c->stream));
@@ -784,9 +800,7 @@ int lgbcu_train_tree(LgbCuContext* c, LgbCuSplitRecord* records, int32_t* num_sp
         ok = launch_hist(c, -1) == 0;
         if (s == 0) LAUNCH(k_root_sums, 1, 32, 0, c->stream, V);
         LAUNCH(k_find_split, dim3(c->F, 2), FS_THREADS, 0, c->stream, V, 0, -1);
-        LAUNCH(k_part_flags, part_grid, PART_THREADS, 0, c->stream, V);
-        LAUNCH(k_part_scan, 1, 1024, 0, c->stream, V, 0);
-        LAUNCH(k_part_scatter, part_grid, PART_THREADS, 0, c->stream, V, 0);
+        ok = ok && launch_partition(c, c->root_count, 0) == 0;
       }
       cudaError_t ce = cudaStreamEndCapture(c->stream, &g);
       g_launches.fetch_add(before - g_launches.load(std::memory_order_relaxed), std::memory_order_relaxed);
@@ -796,7 +810,7 @@ int lgbcu_train_tree(LgbCuContext* c, LgbCuSplitRecord* records, int32_t* num_sp
       if (ce != cudaSuccess) { c->tree_graph = nullptr; return fail("lgbcu_train_tree: graph instantiate failed (%s)", cudaGetErrorString(ce)); }
     }
     CU(cudaGraphLaunch(c->tree_graph, c->stream));
-    g_launches.fetch_add((long long)(L - 1) * 5 + 1, std::memory_order_relaxed);
+    g_launches.fetch_add((long long)(L - 1) * 3 + 1, std::memory_order_relaxed);
     CU(cudaMemcpyAsync(c->h_ctl, c->d_ctl, sizeof(DevCtl), cudaMemcpyDeviceToHost, c->stream));
     CU(cudaMemcpyAsync(c->h_records, c->d_records, sizeof(LgbCuSplitRecord) * (size_t)(L - 1), cudaMemcpyDeviceToHost, c->stream));
     CU(cudaStreamSynchronize(c->stream));
@@ -822,12 +836,12 @@ int lgbcu_train_tree(LgbCuContext* c, LgbCuSplitRecord* records, int32_t* num_sp
     if (prof) CU(cudaEventRecord(c->ev[EV * s + 1], c->stream));
     LAUNCH(k_find_split, dim3(c->F, 2), FS_THREADS, 0, c->stream, V, 0, -1);
     if (prof) CU(cudaEventRecord(c->ev[EV * s + 2], c->stream));
-    LAUNCH(k_part_flags, part_grid, PART_THREADS, 0, c->stream, V);
-    if (prof) CU(cudaEventRecord(c->ev[EV * s + 3], c->stream));
-    LAUNCH(k_part_scan, 1, 1024, 0, c->stream, V, 0);
-    if (prof) CU(cudaEventRecord(c->ev[EV * s + 4], c->stream));
-    LAUNCH(k_part_scatter, part_grid, PART_THREADS, 0, c->stream, V, 0);
-    if (prof) CU(cudaEventRecord(c->ev[EV * s + 5], c->stream));
+    if (launch_partition(c, c->root_count, 0)) return -1;  // flags + scan + scatter in one launch: reported as "flags"
+    if (prof) {
+      CU(cudaEventRecord(c->ev[EV * s + 3], c->stream));
+      CU(cudaEventRecord(c->ev[EV * s + 4], c->stream));
+      CU(cudaEventRecord(c->ev[EV * s + 5], c->stream));
+    }
   }
   CU(cudaGetLastError());
   CU(cudaMemcpyAsync(c->h_ctl, c->d_ctl, sizeof(DevCtl), cudaMemcpyDeviceToHost, c->stream));
@@ -848,6 +862,18 @@ int lgbcu_train_tree(LgbCuContext* c, LgbCuSplitRecord* records, int32_t* num_sp
       }
     }
     c->loop_phase_valid = true;
+    if (const char* path = std::getenv("LGBCU_PROF_DUMP")) {  // per-split phase times, for offline fitting
+      if (FILE* fp = std::fopen(path, "a")) {
+        for (int s = 0; s < n; ++s) {
+          float t[5];
+          for (int k = 0; k < 5; ++k) cudaEventElapsedTime(&t[k], c->ev[EV * s + k], c->ev[EV * s + k + 1]);
+          const int hist_rows = s == 0 ? c->root_count : std::min(records[s - 1].left_count, records[s - 1].right_count);
+          std::fprintf(fp, "%d,%d,%d,%.3f,%.3f,%.3f,%.3f,%.3f\n", s, hist_rows, records[s].left_count + records[s].right_count,
+                       t[0] * 1e3f, t[1] * 1e3f, t[2] * 1e3f, t[3] * 1e3f, t[4] * 1e3f);
+        }
+        std::fclose(fp);
+      }
+    }
   }
   return 0;
 }
@@ -862,6 +888,14 @@ int lgbcu_profile_phases(LgbCuContext* c, double* ms8) {
 }
 
 #ifdef LGBCU_STAGE_TIMERS
+extern "C" int lgbcu_debug_stamps(unsigned long long* out, int n) {
+  cudaDeviceSynchronize();
+  cudaMemcpyFromSymbol(out, g_stamps, sizeof(unsigned long long) * (size_t)n);
+  cudaMemcpyFromSymbol(out + n, g_ends, sizeof(unsigned long long) * (size_t)n);
+  static unsigned long long z[3 * 4096];
+  cudaMemcpyToSymbol(g_ends, z, sizeof(z));
+  return 0;
+}
 extern "C" int lgbcu_debug_stages(unsigned long long* out16, int reset) {
   unsigned long long z[16] = {0};
   cudaDeviceSynchronize();

@@ -100,6 +100,8 @@ __device__ void part_flags_phase(const DevView& V, int bid, int nblocks) {
   }
 }
 
+__device__ void part_control(const DevView& V, int mode, int leaf, const DevLeaf& L, int left_cnt);
+
 // mode 0: training (control step runs); mode 1: step-wise API (only counts/ranges are updated, sums untouched).
 // One block (any multiple of 32 threads up to 1024).
 __device__ void part_scan_phase(const DevView& V, int mode) {
@@ -144,7 +146,13 @@ __device__ void part_scan_phase(const DevView& V, int mode) {
     __syncthreads();
   }
   if (threadIdx.x != 0) return;
-  const int left_cnt = s_carry, right_cnt = L.count - s_carry;
+  part_control(V, mode, leaf, L, s_carry);
+}
+
+// The bookkeeping that follows a partition (one thread): leaf table, split record, smaller/larger, gates.
+__device__ void part_control(const DevView& V, int mode, int leaf, const DevLeaf& L, int left_cnt) {
+  DevCtl* c = V.ctl;
+  const int right_cnt = L.count - left_cnt;
   c->split_left_count = left_cnt;
   const int R = c->split_right_leaf;
   DevLeaf A = L, B = L;  // A = left child (keeps the id), B = right child (new id R)
@@ -256,4 +264,145 @@ __global__ void __launch_bounds__(PART_THREADS) k_part_scatter(DevView V, int un
   if (V.ctl->done == 1) return;
   (void)unused;
   part_scatter_phase(V, blockIdx.x, gridDim.x);
+}
+
+// ---------------------------------------------------------------------------------------------------------------
+// Fused partition: flags -> (inter-block barrier) -> scatter + control in ONE launch.  The three-launch version
+// above spends most of its time in launch ramps and dependent control loads for the typical 10^4..10^5-row leaf;
+// here the only inter-block communication is one left-count per block and one arrive counter.
+//   * blocks [0, P) own contiguous chunks of 1024-row tiles; block P (one extra) is the control block;
+//   * phase 1: decisions -> ballot words (shared memory for a block's first PART_SMEM_TILES tiles, V.part_bits
+//     beyond), block left-count -> V.tile_left[block]; arrive;
+//   * barrier: spin until all P blocks have arrived (the launch is cooperative, so co-residency is guaranteed);
+//   * phase 2: every block sums the counts of the blocks before it (its write offset) and of all blocks (where the
+//     right side starts), then scatters its rows; the control block runs part_control meanwhile.
+// The arrive/depart counters reset themselves: the last block to leave the barrier zeroes both.
+#define PART_SMEM_TILES 8
+__global__ void __launch_bounds__(PART_THREADS) k_partition(DevView V, int mode) {
+  DevCtl* c = V.ctl;
+  if (c->done) return;
+  STAMP(c, 2);
+  const int leaf = c->split_leaf;
+  const DevLeaf L = V.leaves[leaf];
+  const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+  const int ntiles = (L.count + PART_TILE - 1) / PART_TILE;
+  const int maxp = (int)gridDim.x - 1;
+  const int tpb = (ntiles + maxp - 1) / maxp;          // tiles per block
+  const int P = (ntiles + tpb - 1) / tpb;              // blocks that own tiles
+  const int bid = blockIdx.x;
+  if (bid > P) return;
+  const bool control = bid == P;
+  __shared__ unsigned s_bits[PART_SMEM_TILES][PART_TILE / 32];
+  __shared__ int s_cnt[PART_THREADS / 32];
+  __shared__ int s_red[2][PART_THREADS / 32];
+  const int t0 = bid * tpb;
+  int t1 = t0 + tpb; if (t1 > ntiles) t1 = ntiles;
+  const int* src = V.indices[L.buf] + L.begin;
+  int* dst = V.indices[L.buf ^ 1] + L.begin;
+  int row0[PART_REPS];  // rows of the block's first tile stay in registers for the scatter
+  if (!control) {
+    const DevFeat F = V.feats[c->split_feature];
+    const SplitRule rule = make_rule(F, c->split_threshold, c->split_default_left);
+    const uint8_t* col = V.bins + c->split_feature;
+    int lefts = 0;
+    for (int tile = t0; tile < t1; ++tile) {
+      const int lt = tile - t0;
+#pragma unroll
+      for (int r = 0; r < PART_REPS; ++r) {
+        const int pos = tile * PART_TILE + r * PART_THREADS + tid;
+        bool left = false;
+        int row = 0;
+        if (pos < L.count) {
+          row = src[pos];
+          left = goes_left(rule, col[(size_t)row * V.row_stride]);
+        }
+        if (lt == 0) row0[r] = row;
+        const unsigned word = __ballot_sync(0xffffffffu, left);
+        if (lane == 0) {
+          const int wi = r * (PART_THREADS / 32) + warp;
+          if (lt < PART_SMEM_TILES) s_bits[lt][wi] = word;
+          else V.part_bits[(size_t)tile * (PART_TILE / 32) + wi] = word;
+          lefts += __popc(word);
+        }
+      }
+    }
+    if (lane == 0) s_cnt[warp] = lefts;
+    __syncthreads();
+    if (tid == 0) {
+      int t = 0;
+      for (int w = 0; w < PART_THREADS / 32; ++w) t += s_cnt[w];
+      __stcg(&V.tile_left[bid], t);
+      __threadfence();
+      atomicAdd(&c->bar_arrive, 1u);
+    }
+  }
+  if (tid == 0) {
+    while (*reinterpret_cast<volatile unsigned*>(&c->bar_arrive) < (unsigned)P) { }
+    __threadfence();
+  }
+  __syncthreads();
+  // offsets: lefts of the blocks before this one, and of all blocks
+  int before = 0, total = 0;
+  for (int b = tid; b < P; b += PART_THREADS) {
+    const int v = __ldcg(&V.tile_left[b]);
+    total += v;
+    if (b < bid) before += v;
+  }
+  for (int o = 16; o > 0; o >>= 1) {
+    before += __shfl_xor_sync(0xffffffffu, before, o);
+    total += __shfl_xor_sync(0xffffffffu, total, o);
+  }
+  if (lane == 0) { s_red[0][warp] = before; s_red[1][warp] = total; }
+  __syncthreads();
+  before = 0; total = 0;
+#pragma unroll
+  for (int w = 0; w < PART_THREADS / 32; ++w) { before += s_red[0][w]; total += s_red[1][w]; }
+  if (tid == 0) {  // leave the barrier; the last one out re-arms it
+    const unsigned d = atomicAdd(&c->bar_depart, 1u);
+    if (d == (unsigned)P) { c->bar_arrive = 0; c->bar_depart = 0; }
+  }
+#ifdef LGBCU_STAGE_TIMERS
+  const int split_ = V.ctl->num_splits;  // (racy by one against the control block: good enough for a probe)
+#endif
+  if (control) {
+    if (mode == 0) {  // snapshot FeatureHistogram::is_splittable_ of the leaf being split for k_find_split
+      const int8_t* sp = V.splittable + (size_t)L.slot * V.num_features;
+      for (int f = tid; f < V.num_features; f += PART_THREADS) V.parent_split[f] = sp[f];
+    }
+    if (tid == 0) part_control(V, mode, leaf, L, total);
+    return;
+  }
+  const int left_total = total;
+  int tile_off = before;
+  for (int tile = t0; tile < t1; ++tile) {
+    const int lt = tile - t0;
+    const unsigned myword = lt < PART_SMEM_TILES ? s_bits[lt][lane] : V.part_bits[(size_t)tile * (PART_TILE / 32) + lane];
+    const int pc = __popc(myword);
+    int inc = pc;
+    for (int o = 1; o < 32; o <<= 1) {
+      const int x = __shfl_up_sync(0xffffffffu, inc, o);
+      if (lane >= o) inc += x;
+    }
+    const int excl = inc - pc;
+    const int tile_total = __shfl_sync(0xffffffffu, inc, 31);
+#pragma unroll
+    for (int r = 0; r < PART_REPS; ++r) {
+      const int w = r * (PART_THREADS / 32) + warp;
+      const unsigned word = __shfl_sync(0xffffffffu, myword, w);
+      const int wpre = __shfl_sync(0xffffffffu, excl, w);
+      const int pos = tile * PART_TILE + w * 32 + lane;
+      if (pos < L.count) {
+        const unsigned ltm = (1u << lane) - 1u;
+        const int row = lt == 0 ? row0[r] : src[pos];
+        if ((word >> lane) & 1u) {
+          dst[tile_off + wpre + __popc(word & ltm)] = row;
+        } else {
+          const int rights_before = (tile * PART_TILE - tile_off) + (w * 32 - wpre) + __popc(~word & ltm);
+          dst[left_total + rights_before] = row;
+        }
+      }
+    }
+    tile_off += tile_total;
+  }
+  STAMP_END(split_, 2);
 }

@@ -630,6 +630,7 @@ __global__ void __launch_bounds__(FS_THREADS) k_find_split(DevView V, int mode, 
   DevCtl* c = V.ctl;
   if (mode == 0 && c->done) return;
   STAGE_BEGIN();
+  STAMP(c, 1);
   const bool active = (mode == 1) || !c->skip_find;
   const int smaller = (mode == 1) ? leaf_arg : c->smaller;
   const int larger = (mode == 1) ? -1 : c->larger;
@@ -644,6 +645,7 @@ __global__ void __launch_bounds__(FS_THREADS) k_find_split(DevView V, int mode, 
   }
   __syncthreads();
   STAGE(5);
+  STAMP_END(c->num_splits, 1);
 #ifdef LGBCU_STAGE_TIMERS
   long long tc0 = clock64();
   if (s_last && threadIdx.x < 32) { if (threadIdx.x == 0) c->feat_done = 0; find_control(V, mode, active, smaller, larger);

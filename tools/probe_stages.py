@@ -23,3 +23,21 @@ for rep in range(3):
     t0 = time.time(); recs = L.train_tree(); dt = time.time() - t0
     lib.lgbcu_debug_stages(out, 0)
     print(f"tree {dt*1e3:.2f} ms; find stages (us per call @1.9GHz): ", [round(out[i] / 1.9e3 / max(1, len(recs)), 2) for i in range(8)])
+# per-split start stamps of the three kernels (graph path): deltas = kernel duration + gap
+ns = len(recs)
+st = (ctypes.c_ulonglong * (6 * ns))()
+lib.lgbcu_debug_stamps(st, 3 * ns)
+a = np.array(list(st)[:3 * ns], dtype=np.float64).reshape(ns, 3)
+e = np.array(list(st)[3 * ns:], dtype=np.float64).reshape(ns, 3)
+ex = e - a   # execution: first block start -> last block exit
+print("exec-only means us: hist %.2f find(to ticket) %.2f part %.2f" % tuple(np.median(ex, axis=0) / 1e3))
+hist = a[:, 1] - a[:, 0]; find = a[:, 2] - a[:, 1]; part = np.append(a[1:, 0] - a[:-1, 2], np.nan)
+rows = np.array([n] + [min(r.left_count, r.right_count) for r in recs[:-1]])
+prow = np.array([r.left_count + r.right_count for r in recs])
+print("totals ms: hist %.2f find %.2f part %.2f" % (hist.sum() / 1e6, find.sum() / 1e6, np.nansum(part) / 1e6))
+for lo, hi in [(0, 4096), (4096, 20000), (20000, 100000), (100000, 500000), (500000, 2e6), (2e6, 2e7)]:
+    m = (rows >= lo) & (rows < hi)
+    if m.sum(): print(f"hist rows [{lo:.0f},{hi:.0f}) n={m.sum():3d} mean rows {rows[m].mean():9.0f} hist {hist[m].mean()/1e3:7.2f}us (exec {ex[m,0].mean()/1e3:6.2f}) find {find[m].mean()/1e3:6.2f}us (exec {ex[m,1].mean()/1e3:6.2f})")
+for lo, hi in [(0, 20000), (20000, 100000), (100000, 500000), (500000, 2e6), (2e6, 2e7)]:
+    m = (prow >= lo) & (prow < hi)
+    if m.sum(): print(f"part rows [{lo:.0f},{hi:.0f}) n={m.sum():3d} mean {prow[m].mean():9.0f} part {np.nanmean(part[m])/1e3:6.2f}us (exec {ex[m,2].mean()/1e3:6.2f})")
