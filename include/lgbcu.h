@@ -229,9 +229,8 @@ LGBCU_API int lgbcu_profile_enable(LgbCuContext* ctx, int on);
 LGBCU_API int lgbcu_profile_read(LgbCuContext* ctx, double* hist_ms, int64_t* hist_calls, double* hist_bytes,
                                  int reset);
 
-/* persistent tree-growing kernel, profile mode: milliseconds of the LAST tree spent in each phase including the
- * grid barrier that ends it: [0] histogram [1] root sums [2] split search [3] control [4] partition flags
- * [5] partition scan + bookkeeping [6] scatter [7] unused */
+/* profile mode: milliseconds of the LAST tree spent in each phase (CUDA events around every launch of the
+ * per-split sequence): [0] histogram (+ all-reduce) [2] split search + control [4] partition; other slots 0 */
 LGBCU_API int lgbcu_profile_phases(LgbCuContext* ctx, double* ms8);
 
 #ifdef __cplusplus

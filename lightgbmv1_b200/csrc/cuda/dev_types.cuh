@@ -76,7 +76,6 @@ struct DevCtl {
   long long global_rows;  // dataset rows over all ranks }
   unsigned bar_depart, pad1;
   unsigned long long prof_hist_rows, prof_hist_rows_indexed, prof_hist_calls, prof_hist_ns;
-  unsigned long long prof_phase_ns[8];  // persistent kernel: hist, root, find, control, flags, scan, scatter, (spare)
 };
 
 struct DevParams {   // LgbCuTreeParams + derived switches

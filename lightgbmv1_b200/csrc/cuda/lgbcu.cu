@@ -19,7 +19,6 @@
 #include "split_kernels.cuh"
 #include "partition_kernels.cuh"
 #include "misc_kernels.cuh"
-#include "grow_kernel.cuh"
 
 namespace {
 
@@ -116,9 +115,9 @@ struct LgbCuContext {
   // config
   int hist_mode = LGBCU_HIST_AUTO;
   int hist_min_rows = HIST_MIN_ROWS_PER_WARP;
+  int hist_small_rows = HIST_SMALL_LEAF_ROWS;
   bool force_dp_counts = false;  // LGBCU_FORCE_DP_COUNTS=1: single rank, but leaf counts as in data-parallel mode (tests)
   cudaGraphExec_t tree_graph = nullptr; bool use_graph = true;  // the per-tree launch sequence, captured once
-  bool persistent_ok = false, use_persistent = false;  // launch-per-phase loop measured faster (profiles/r1_c); LGBCU_PERSISTENT=1 selects k_grow_tree
   int objective = LGBCU_OBJ_NONE; double obj_p[3] = {0, 0, 0};
   int root_count = 0; bool tree_begun = false;
   // profiling
@@ -179,7 +178,7 @@ int ensure_tree_buffers(LgbCuContext* c) {
 
 int launch_hist(LgbCuContext* c, int leaf_arg) {
   const DevView V = c->view();
-  LAUNCH(k_hist, c->num_sms, HIST_THREADS, HIST_SMEM_BYTES, c->stream, V, leaf_arg, c->hist_mode, c->hist_min_rows);
+  LAUNCH(k_hist, c->num_sms * HIST_BLOCKS_PER_SM, HIST_THREADS, HIST_SMEM_BYTES, c->stream, V, leaf_arg, c->hist_mode, c->hist_min_rows, c->hist_small_rows);
   CU(cudaGetLastError());
   return 0;
 }
@@ -259,7 +258,8 @@ int lgbcu_create(int device_id, LgbCuContext** out) {
   cudaDeviceProp prop;
   CU(cudaGetDeviceProperties(&prop, device_id));
   c->num_sms = prop.multiProcessorCount;
-  if (const char* e = std::getenv("LGBCU_HIST_MIN_ROWS")) { const int v = std::atoi(e); if (v >= 32) c->hist_min_rows = v; }
+  if (const char* e = std::getenv("LGBCU_HIST_MIN_ROWS")) { const int v = std::atoi(e); if (v >= 1) c->hist_min_rows = v; }
+  if (const char* e = std::getenv("LGBCU_HIST_SMALL_ROWS")) { const int v = std::atoi(e); if (v >= 0) c->hist_small_rows = v; }
   CU(cudaStreamCreateWithFlags(&c->stream, cudaStreamNonBlocking));
   CU(dev_alloc(&c->d_ctl, 1));
   CU(cudaMemset(c->d_ctl, 0, sizeof(DevCtl)));
@@ -267,13 +267,10 @@ int lgbcu_create(int device_id, LgbCuContext** out) {
   CU(cudaMallocHost(reinterpret_cast<void**>(&c->h_leaf), sizeof(DevLeaf)));
   CU(cudaMallocHost(reinterpret_cast<void**>(&c->h_split), sizeof(DevSplit)));
   CU(cudaFuncSetAttribute(k_hist, cudaFuncAttributeMaxDynamicSharedMemorySize, HIST_SMEM_BYTES));
-  CU(cudaFuncSetAttribute(k_grow_tree, cudaFuncAttributeMaxDynamicSharedMemorySize, HIST_SMEM_BYTES));
   {
-    int coop = 0, per_sm = 0;
+    int coop = 0;
     CU(cudaDeviceGetAttribute(&coop, cudaDevAttrCooperativeLaunch, device_id));
-    CU(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, k_grow_tree, GROW_THREADS, HIST_SMEM_BYTES));
-    c->persistent_ok = coop != 0 && per_sm >= 1;
-    if (const char* e = std::getenv("LGBCU_PERSISTENT")) c->use_persistent = std::atoi(e) != 0;
+    NEED(coop != 0, "lgbcu_create: device %d cannot do cooperative launches (needed by the fused partition)", device_id);
     if (const char* e = std::getenv("LGBCU_GRAPH")) c->use_graph = std::atoi(e) != 0;
     if (const char* e = std::getenv("LGBCU_FORCE_DP_COUNTS")) c->force_dp_counts = std::atoi(e) != 0;
   }
@@ -769,26 +766,7 @@ int lgbcu_train_tree(LgbCuContext* c, LgbCuSplitRecord* records, int32_t* num_sp
   CU(cudaSetDevice(c->device));
   const DevView V = c->view();
   const int L = c->params.num_leaves;
-  const int part_grid = grid_for(c, c->root_count, PART_TILE);
   const bool prof = c->profile;
-  if (c->use_persistent && c->persistent_ok && !c->comm) {
-    // one cooperative launch grows the whole tree (grow_kernel.cuh)
-    DevView Vv = V; int hm = c->hist_mode, mr = c->hist_min_rows, pf = prof ? (std::getenv("LGBCU_PROF_SYNC") ? 2 : 1) : 0;
-    void* args[] = {&Vv, &hm, &mr, &pf};
-    if (prof) CU(cudaMemsetAsync(&c->d_ctl->prof_hist_ns, 0, 9 * sizeof(unsigned long long), c->stream));
-    CU(cudaLaunchCooperativeKernel(reinterpret_cast<void*>(k_grow_tree), dim3(c->num_sms), dim3(GROW_THREADS), args,
-                                   HIST_SMEM_BYTES, c->stream));
-    g_launches.fetch_add(1, std::memory_order_relaxed);
-    CU(cudaMemcpyAsync(c->h_ctl, c->d_ctl, sizeof(DevCtl), cudaMemcpyDeviceToHost, c->stream));
-    CU(cudaMemcpyAsync(c->h_records, c->d_records, sizeof(LgbCuSplitRecord) * (size_t)(L - 1), cudaMemcpyDeviceToHost, c->stream));
-    CU(cudaStreamSynchronize(c->stream));
-    const int n = c->h_ctl->num_splits;
-    NEED(n >= 0 && n <= L - 1, "lgbcu_train_tree: corrupt split count %d", n);
-    std::memcpy(records, c->h_records, sizeof(LgbCuSplitRecord) * (size_t)n);
-    *num_splits = n;
-    if (prof) c->prof_hist_ms += (double)c->h_ctl->prof_hist_ns * 1e-6;
-    return 0;
-  }
   if (c->use_graph && !prof && !c->comm) {
     // the launch sequence of a tree is fixed (all sizes are read on the device): capture it once, replay per tree
     if (!c->tree_graph) {
@@ -883,7 +861,7 @@ int lgbcu_profile_phases(LgbCuContext* c, double* ms8) {
   CU(cudaSetDevice(c->device));
   CU(cudaMemcpyAsync(c->h_ctl, c->d_ctl, sizeof(DevCtl), cudaMemcpyDeviceToHost, c->stream));
   CU(cudaStreamSynchronize(c->stream));
-  for (int i = 0; i < 8; ++i) ms8[i] = c->loop_phase_valid ? c->loop_phase_ms[i] : (double)c->h_ctl->prof_phase_ns[i] * 1e-6;
+  for (int i = 0; i < 8; ++i) ms8[i] = c->loop_phase_valid ? c->loop_phase_ms[i] : 0.0;
   return 0;
 }
 
