@@ -4,7 +4,7 @@
 NVCC     ?= /usr/local/cuda/bin/nvcc
 CXX      := $(shell command -v /usr/bin/g++ || echo g++)
 ARCH     := -gencode arch=compute_100a,code=sm_100a
-NVFLAGS  := $(ARCH) -lineinfo -O3 --fmad=false -std=c++17 -Xcompiler -fPIC -Iinclude -ccbin $(CXX)
+NVFLAGS  := $(ARCH) -lineinfo -O3 --fmad=false -std=c++17 -Xcompiler -fPIC -Xcompiler -fopenmp -Iinclude -ccbin $(CXX)
 CXXFLAGS := -std=c++17 -O2 -fPIC -fvisibility=hidden -fopenmp -Wall -Wextra -Wno-unused-parameter -Iinclude
 PKG      := lightgbmv1_b200
 CUDA_SRC := $(PKG)/csrc/cuda/lgbcu.cu

@@ -25,6 +25,7 @@
 #ifndef LGBCU_H_
 #define LGBCU_H_
 
+#include <stddef.h>
 #include <stdint.h>
 
 #ifdef __cplusplus
@@ -107,6 +108,12 @@ typedef struct LgbCuSplitRecord {
 LGBCU_API const char* lgbcu_last_error(void);
 /* number of CUDA devices visible (0 if none / no driver) */
 LGBCU_API int lgbcu_device_count(int* out);
+/* Page-lock (cudaHostRegister) / release a host buffer that will be uploaded with lgbcu_set_dataset, so that the
+ * copy runs at full PCIe rate instead of through the driver's pageable staging.  Returns -1 (buffer stays pageable,
+ * everything still works) when there is no device or the registration fails.  No reference counterpart: the
+ * reference's CPU learner never copies its bin matrix anywhere. */
+LGBCU_API int lgbcu_pin_host_buffer(void* ptr, size_t bytes);
+LGBCU_API int lgbcu_unpin_host_buffer(void* ptr);
 /* number of kernels launched by this library in this process (bench.py's gpu_launches) */
 LGBCU_API int64_t lgbcu_launch_count(void);
 

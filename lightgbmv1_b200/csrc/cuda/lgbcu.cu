@@ -82,6 +82,7 @@ struct LgbCuContext {
   bool has_weight = false, has_label = false;
   double* d_score = nullptr;
   int* d_indices[2] = {nullptr, nullptr};
+  double* h_stage[2] = {nullptr, nullptr}; cudaEvent_t stage_ev[2] = {nullptr, nullptr};  // D2H staging of lgbcu_copy_score
   unsigned* d_part_bits = nullptr;
   int* d_tile_left = nullptr;
   // query structure (lambdarank)
@@ -240,6 +241,20 @@ int lgbcu_device_count(int* out) {
   return 0;
 }
 
+int lgbcu_pin_host_buffer(void* ptr, size_t bytes) {
+  if (!ptr || bytes == 0) return -1;
+  int n = 0;
+  if (cudaGetDeviceCount(&n) != cudaSuccess || n == 0) { cudaGetLastError(); return -1; }
+  if (cudaHostRegister(ptr, bytes, cudaHostRegisterPortable) != cudaSuccess) { cudaGetLastError(); return -1; }
+  return 0;
+}
+
+int lgbcu_unpin_host_buffer(void* ptr) {
+  if (!ptr) return -1;
+  if (cudaHostUnregister(ptr) != cudaSuccess) { cudaGetLastError(); return -1; }
+  return 0;
+}
+
 int64_t lgbcu_launch_count(void) { return g_launches.load(); }
 
 int lgbcu_create(int device_id, LgbCuContext** out) {
@@ -294,6 +309,7 @@ int lgbcu_destroy(LgbCuContext* c) {
   if (c->h_ctl) cudaFreeHost(c->h_ctl);
   if (c->h_leaf) cudaFreeHost(c->h_leaf);
   if (c->h_split) cudaFreeHost(c->h_split);
+  for (int i = 0; i < 2; ++i) { if (c->h_stage[i]) cudaFreeHost(c->h_stage[i]); if (c->stage_ev[i]) cudaEventDestroy(c->stage_ev[i]); }
   for (auto e : c->ev) cudaEventDestroy(e);
   cudaStreamDestroy(c->stream);
   delete c;
@@ -538,8 +554,41 @@ int lgbcu_add_score_const(LgbCuContext* c, double val) {
 int lgbcu_copy_score(LgbCuContext* c, double* score, int32_t n) {
   NEED(c && score && n == c->N, "lgbcu_copy_score: bad argument");
   CU(cudaSetDevice(c->device));
-  CU(cudaMemcpyAsync(score, c->d_score, sizeof(double) * n, cudaMemcpyDeviceToHost, c->stream));
-  CU(cudaStreamSynchronize(c->stream));
+  // The caller's buffer is pageable (and usually untouched): stream the scores through two page-locked staging
+  // buffers and let the host threads move each chunk on while the next one is in flight.
+  const size_t CH = (size_t)1 << 19;  // doubles per chunk (4 MB)
+  if ((size_t)n <= CH) {
+    CU(cudaMemcpyAsync(score, c->d_score, sizeof(double) * n, cudaMemcpyDeviceToHost, c->stream));
+    CU(cudaStreamSynchronize(c->stream));
+    return 0;
+  }
+  if (!c->h_stage[0]) {
+    for (int i = 0; i < 2; ++i) {
+      CU(cudaMallocHost(reinterpret_cast<void**>(&c->h_stage[i]), CH * sizeof(double)));
+      CU(cudaEventCreateWithFlags(&c->stage_ev[i], cudaEventDisableTiming));
+    }
+  }
+  const size_t nchunk = ((size_t)n + CH - 1) / CH;
+  auto chunk_len = [&](size_t k) { return std::min(CH, (size_t)n - k * CH); };
+  CU(cudaMemcpyAsync(c->h_stage[0], c->d_score, sizeof(double) * chunk_len(0), cudaMemcpyDeviceToHost, c->stream));
+  CU(cudaEventRecord(c->stage_ev[0], c->stream));
+  for (size_t k = 0; k < nchunk; ++k) {
+    const int cur = (int)(k & 1), nxt = cur ^ 1;
+    if (k + 1 < nchunk) {
+      CU(cudaMemcpyAsync(c->h_stage[nxt], c->d_score + (k + 1) * CH, sizeof(double) * chunk_len(k + 1), cudaMemcpyDeviceToHost, c->stream));
+      CU(cudaEventRecord(c->stage_ev[nxt], c->stream));
+    }
+    CU(cudaEventSynchronize(c->stage_ev[cur]));
+    const size_t len = chunk_len(k);
+    double* dst = score + k * CH;
+    const double* src = c->h_stage[cur];
+    const long long pieces = (long long)((len + 32767) / 32768);
+#pragma omp parallel for schedule(static)
+    for (long long p = 0; p < pieces; ++p) {
+      const size_t a = (size_t)p * 32768, b = std::min(len, a + 32768);
+      std::memcpy(dst + a, src + a, (b - a) * sizeof(double));
+    }
+  }
   return 0;
 }
 

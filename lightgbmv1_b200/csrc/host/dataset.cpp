@@ -5,6 +5,7 @@
 #include <algorithm>
 #include <cstring>
 
+#include "lgbcu.h"
 #include "random.h"
 
 namespace lgb {
@@ -242,6 +243,12 @@ void Dataset::BinAllRows(const void* data, int data_type, int32_t nrow, int32_t 
     uint8_t* out = bins_.data() + static_cast<size_t>(r) * F;
     for (int f = 0; f < F; ++f) out[f] = static_cast<uint8_t>(stored_value(f, M.at(r, inner_to_real_[f])));
   }
+  // the matrix only exists to be uploaded: page-lock it (a no-op without a device)
+  bins_pinned_ = lgbcu_pin_host_buffer(bins_.data(), bins_.size()) == 0;
+}
+
+Dataset::~Dataset() {
+  if (bins_pinned_) lgbcu_unpin_host_buffer(bins_.data());
 }
 
 uint64_t Dataset::num_total_bin() const {

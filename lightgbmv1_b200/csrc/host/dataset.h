@@ -29,6 +29,10 @@ class Dataset {
   static Dataset* FromDenseMatrixAligned(const void* data, int data_type, int32_t nrow, int32_t ncol, bool row_major,
                                          const Dataset& reference);
 
+  ~Dataset();
+  Dataset(const Dataset&) = delete;
+  Dataset& operator=(const Dataset&) = delete;
+
   data_size_t num_data() const { return num_data_; }
   int num_features() const { return static_cast<int>(inner_to_real_.size()); }
   int num_total_features() const { return num_total_features_; }
@@ -57,6 +61,7 @@ class Dataset {
   std::vector<std::shared_ptr<BinMapper>> mappers_;  // per inner feature
   std::vector<int> inner_to_real_, real_to_inner_;
   std::vector<uint8_t> bins_;
+  bool bins_pinned_ = false;  // page-locked for the upload (lgbcu_pin_host_buffer)
   std::vector<std::string> feature_names_;
   Metadata meta_;
 };

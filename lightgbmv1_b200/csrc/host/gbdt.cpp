@@ -1,4 +1,7 @@
 #include "gbdt.h"
+#include <chrono>
+#include <cstdio>
+#include <cstdlib>
 
 #include <omp.h>
 
@@ -17,6 +20,17 @@ void Check(int rc) {
   if (rc != 0) Log::Fatal("%s", lgbcu_last_error());
 }
 const int kBaggingRandBlock = 1024;  // gbdt.h:519
+// LGBM_B200_TIMING=1: wall-clock of the host-side stages on stderr (where does an end-to-end call spend its time)
+struct StageTimer {
+  bool on; std::chrono::steady_clock::time_point t;
+  StageTimer() : on(std::getenv("LGBM_B200_TIMING") != nullptr), t(std::chrono::steady_clock::now()) {}
+  void tick(const char* what) {
+    if (!on) return;
+    const auto n = std::chrono::steady_clock::now();
+    std::fprintf(stderr, "[b200 timing] %-28s %8.2f ms\n", what, std::chrono::duration<double, std::milli>(n - t).count());
+    t = n;
+  }
+};
 }  // namespace
 
 GBDT::GBDT(const Dataset* train, const Config& config)
@@ -24,6 +38,7 @@ GBDT::GBDT(const Dataset* train, const Config& config)
       feature_rand_(config.feature_fraction_seed) {
   const int N = train_->num_data(), F = train_->num_features();
   if (F <= 0) Log::Fatal("the CUDA learner needs at least one non-constant feature");
+  StageTimer st;
   objective_.reset(Objective::Create(config_));
   if (objective_) {
     objective_->Init(train_->metadata(), N);
@@ -34,7 +49,9 @@ GBDT::GBDT(const Dataset* train, const Config& config)
   lgbcu_device_count(&ndev);
   int dev = config_.gpu_device_id >= 0 ? config_.gpu_device_id : 0;
   if (Net().active && config_.gpu_device_id < 0 && ndev > 0) dev = Net().rank % ndev;
+  st.tick("objective init");
   Check(lgbcu_create(dev, &ctx_));
+  st.tick("lgbcu_create");
   std::vector<LgbCuFeatureMeta> meta(F);
   for (int f = 0; f < F; ++f) {
     const BinMapper& m = train_->mapper(f);
@@ -46,6 +63,7 @@ GBDT::GBDT(const Dataset* train, const Config& config)
   if (!config_.feature_contri.empty() && static_cast<int>(config_.feature_contri.size()) != train_->num_total_features())
     Log::Fatal("Check failed: feature_contri size");
   Check(lgbcu_set_dataset(ctx_, N, F, train_->bins().data(), meta.data()));
+  st.tick("lgbcu_set_dataset");
   LgbCuTreeParams tp;
   tp.num_leaves = config_.num_leaves; tp.max_depth = config_.max_depth; tp.min_data_in_leaf = config_.min_data_in_leaf;
   tp.reserved = 0; tp.min_sum_hessian_in_leaf = config_.min_sum_hessian_in_leaf; tp.lambda_l1 = config_.lambda_l1;
@@ -53,6 +71,7 @@ GBDT::GBDT(const Dataset* train, const Config& config)
   tp.max_delta_step = config_.max_delta_step; tp.path_smooth = config_.path_smooth;
   Check(lgbcu_set_tree_params(ctx_, &tp));
   Check(lgbcu_set_hist_mode(ctx_, config_.hist_mode));
+  st.tick("lgbcu_set_tree_params");
   const Metadata& md = train_->metadata();
   if (!md.label.empty()) Check(lgbcu_set_label(ctx_, md.label.data(), N));
   if (!md.weights.empty()) Check(lgbcu_set_weight(ctx_, md.weights.data(), N));
@@ -64,6 +83,7 @@ GBDT::GBDT(const Dataset* train, const Config& config)
     Check(lgbcu_comm_init(ctx_, Net().unique_id, Net().rank, Net().num_machines));
   }
   records_.resize(std::max(config_.num_leaves - 1, 1));
+  st.tick("labels/objective/comm");
 
   // ---- ResetBaggingConfig (gbdt.cpp:739-797)
   if (config_.bagging_fraction < 1.0 && config_.bagging_freq > 0) {
@@ -125,6 +145,7 @@ void GBDT::Bagging(int iter) {
 bool GBDT::TrainOneIter(const float* grad, const float* hess) {
   const int N = train_->num_data();
   double init_score = 0.0;
+  StageTimer st;
   if (grad == nullptr || hess == nullptr) {
     if (!objective_) Log::Fatal("No object function provided");
     // BoostFromAverage (gbdt.cpp:312-335)
@@ -140,6 +161,7 @@ bool GBDT::TrainOneIter(const float* grad, const float* hess) {
         Log::Info("Start training from score %lf", init_score);
       }
     }
+    st.tick("boost from average");
     Check(lgbcu_get_gradients(ctx_));  // GBDT::Boosting
   } else {
     Check(lgbcu_set_gradients(ctx_, grad, hess, N));
@@ -154,7 +176,9 @@ bool GBDT::TrainOneIter(const float* grad, const float* hess) {
     Check(lgbcu_begin_tree(ctx_, bagged ? bag_indices_.data() : nullptr, bagged ? bag_cnt_ : 0,
                            need_reset_bytree_ ? feature_used_.data() : nullptr));
     int ns = 0;
+    st.tick("gradients/bagging/begin_tree");
     Check(lgbcu_train_tree(ctx_, records_.data(), &ns));
+    st.tick("lgbcu_train_tree");
     tree.reset(new Tree(config_.num_leaves));
     for (int i = 0; i < ns; ++i) {
       const LgbCuSplitRecord& r = records_[i];
@@ -185,6 +209,7 @@ bool GBDT::TrainOneIter(const float* grad, const float* hess) {
       Check(lgbcu_add_score_const(ctx_, output));
     }
   }
+  st.tick("tree + score update");
   models_.push_back(std::move(tree));
   if (!should_continue) {
     Log::Warning("Stopped training because there are no more leaves that meet the split requirements");

@@ -20,7 +20,9 @@ class BinaryLogloss : public Objective {
     num_data_ = n; label_ = meta.label.data(); weights_ = meta.weights.empty() ? nullptr : meta.weights.data();
     if (meta.label.empty()) Log::Fatal("Label should not be NULL");
     data_size_t pos = 0, neg = 0;
+#pragma omp parallel for schedule(static) reduction(+:pos, neg)
     for (data_size_t i = 0; i < n; ++i) { if (label_[i] > 0) ++pos; else ++neg; }
+    num_pos_ = pos;
     need_train_ = !(neg == 0 || pos == 0);
     if (!need_train_) Log::Warning("Contains only one class");
     Log::Info("Number of positive: %d, number of negative: %d", pos, neg);
@@ -36,11 +38,12 @@ class BinaryLogloss : public Objective {
   }
   double BoostFromScore() const override {
     double suml = 0.0f, sumw = 0.0f;
-    if (weights_) {
+    if (weights_) {  // (the reference reduces over OpenMP threads too: binary_objective.hpp BoostFromScore)
+#pragma omp parallel for schedule(static) reduction(+:suml, sumw)
       for (data_size_t i = 0; i < num_data_; ++i) { suml += (label_[i] > 0) * weights_[i]; sumw += weights_[i]; }
     } else {
       sumw = static_cast<double>(num_data_);
-      for (data_size_t i = 0; i < num_data_; ++i) suml += (label_[i] > 0);
+      suml = static_cast<double>(num_pos_);  // a count: exact in any order
     }
     double pavg = suml / sumw;
     pavg = std::min(pavg, 1.0 - kEpsilon);
@@ -56,7 +59,7 @@ class BinaryLogloss : public Objective {
 
  private:
   double sigmoid_; bool is_unbalance_; double scale_pos_weight_;
-  data_size_t num_data_ = 0; const label_t* label_ = nullptr; const label_t* weights_ = nullptr;
+  data_size_t num_data_ = 0, num_pos_ = 0; const label_t* label_ = nullptr; const label_t* weights_ = nullptr;
   bool need_train_ = true; double label_weights_[2] = {1, 1};
 };
 
@@ -73,10 +76,12 @@ class RegressionL2 : public Objective {
   void Configure(LgbCuContext* ctx) const override { Check(lgbcu_set_objective(ctx, LGBCU_OBJ_L2, 0, 0, 0)); }
   double BoostFromScore() const override {
     double suml = 0.0f, sumw = 0.0f;
-    if (weights_) {
+    if (weights_) {  // (OpenMP reductions as in regression_objective.hpp BoostFromScore)
+#pragma omp parallel for schedule(static) reduction(+:suml, sumw)
       for (data_size_t i = 0; i < num_data_; ++i) { suml += label_[i] * weights_[i]; sumw += weights_[i]; }
     } else {
       sumw = static_cast<double>(num_data_);
+#pragma omp parallel for schedule(static) reduction(+:suml)
       for (data_size_t i = 0; i < num_data_; ++i) suml += label_[i];
     }
     return suml / sumw;
