@@ -72,15 +72,42 @@ __device__ __forceinline__ Cand cand_better(const Cand& a, const Cand& b, bool p
   return take_b ? b : a;
 }
 
-// Only (gain, t) travel through the reduction; the winner's sums are looked up again afterwards.
+// Warp arg-max with the hardware reductions (REDUX on 32-bit integers): a double is mapped to an order-preserving
+// 64-bit key, the maximum is found on its high word, then on the low word among the lanes still tied, then the
+// smallest `tie` (and `tie2`) among those.  Four or five warp collectives instead of five shuffle rounds of compare
+// logic.  Returns the winning lane, or -1 when no lane is valid.  NaN gains must be passed as invalid.
+__device__ __forceinline__ void gain_key(double g, unsigned& hi, unsigned& lo) {
+  unsigned long long u = (unsigned long long)__double_as_longlong(g);
+  u = (u >> 63) ? ~u : (u | 0x8000000000000000ull);
+  hi = (unsigned)(u >> 32); lo = (unsigned)u;
+}
+__device__ __forceinline__ int warp_argmax(double gain, unsigned tie, unsigned tie2, bool valid) {
+  unsigned hi, lo;
+  gain_key(gain, hi, lo);
+  bool a = valid;
+  const unsigned m1 = __reduce_max_sync(FULL_MASK, a ? hi : 0u);
+  a = a && hi == m1;
+  const unsigned m2 = __reduce_max_sync(FULL_MASK, a ? lo : 0u);
+  a = a && lo == m2;
+  const unsigned m3 = __reduce_min_sync(FULL_MASK, a ? tie : 0xffffffffu);
+  a = a && tie == m3;
+  const unsigned m4 = __reduce_min_sync(FULL_MASK, a ? tie2 : 0xffffffffu);
+  a = a && tie2 == m4;
+  const unsigned b = __ballot_sync(FULL_MASK, a);
+  return b ? __ffs(b) - 1 : -1;
+}
+
+// Best threshold candidate of a warp: larger gain, ties -> higher t (reverse scan) / lower t (forward scan).
+// Only (gain, t) are reduced; the winner's sums are looked up again afterwards.
 __device__ __forceinline__ Cand warp_best_cand(Cand c, bool prefer_high) {
-  for (int o = 16; o > 0; o >>= 1) {
-    Cand x = c;
-    x.gain = __shfl_xor_sync(FULL_MASK, c.gain, o);
-    x.t = __shfl_xor_sync(FULL_MASK, c.t, o);
-    c = cand_better(c, x, prefer_high);
-  }
-  return c;
+  const bool valid = c.gain > LGB_MIN_SCORE;  // false for NaN as well: a NaN gain never wins in the reference either
+  const unsigned tie = prefer_high ? (unsigned)(0x40000000 - c.t) : (unsigned)(c.t + 0x40000000);
+  const int w = warp_argmax(c.gain, tie, 0u, valid);
+  Cand r = c;
+  if (w < 0) { r.gain = LGB_MIN_SCORE; r.t = prefer_high ? -1000 : 100000; return r; }
+  r.gain = __shfl_sync(FULL_MASK, c.gain, w);
+  r.t = __shfl_sync(FULL_MASK, c.t, w);
+  return r;
 }
 
 __device__ __forceinline__ i64 warp_sum(i64 v) {
@@ -334,12 +361,18 @@ __device__ void scan_feature_block(ScanSmem& S, int nt, const DevFeat& F, double
   splittable = __any_sync(FULL_MASK, splittable);
   if (lane == 0) { S.wbest[0][warp] = rb; S.wbest[1][warp] = fb; S.wsplit[warp] = splittable; }
   __syncthreads();
-  if (tid != 0) return;
-  int any_split = 0;
-  for (int w = 0; w < FS_WARPS; ++w) {
-    any_split |= S.wsplit[w];
-    if (w) { rb = cand_better(rb, S.wbest[0][w], true); fb = cand_better(fb, S.wbest[1][w], false); }
+  if (warp != 0) return;
+  {
+    Cand x; x.gain = LGB_MIN_SCORE; x.t = -1000; x.left_g = 0; x.left_h = 0; x.left_count = 0;
+    Cand y = x; y.t = 100000;
+    int sp = 0;
+    if (lane < FS_WARPS) { x = S.wbest[0][lane]; y = S.wbest[1][lane]; sp = S.wsplit[lane]; }
+    rb = warp_best_cand(x, true);
+    fb = warp_best_cand(y, false);
+    splittable = __any_sync(FULL_MASK, sp);
   }
+  if (tid != 0) return;
+  const int any_split = splittable;
   // the winners' sums, formed exactly as the evaluating thread formed them
   if (rb.gain > LGB_MIN_SCORE) {
     rb.left_count = num_data - S.RC[rb.t]; rb.left_h = sum_h - S.RH[rb.t]; rb.left_g = sum_g - S.RG[rb.t];
@@ -550,13 +583,16 @@ __device__ void find_control(const DevView& V, int mode, bool active, int smalle
         const SplitKey k = V.feat_key[sel * F + j];
         if (split_better(k.gain, k.real_feature, bg, bf)) { bg = k.gain; bf = k.real_feature; bp = k.pad; bi = j; }
       }
-      for (int o = 16; o > 0; o >>= 1) {
-        const double g2 = __shfl_xor_sync(FULL_MASK, bg, o);
-        const int f2 = __shfl_xor_sync(FULL_MASK, bf, o);
-        const int i2 = __shfl_xor_sync(FULL_MASK, bi, o);
-        const int p2 = __shfl_xor_sync(FULL_MASK, bp, o);
-        // (gain, feature) is a total order over distinct features, so every lane converges to the same winner
-        if (i2 >= 0 && (bi < 0 || split_better(g2, f2, bg, bf))) { bg = g2; bf = f2; bi = i2; bp = p2; }
+      {  // (gain, feature) is a total order over distinct features: one winner
+        const unsigned tie = bf == -1 ? 0x7fffffffu : (unsigned)bf;
+        const int w = warp_argmax(bg, tie, 0u, bi >= 0 && bg == bg);
+        const int src = w < 0 ? 0 : w;
+        bg = __shfl_sync(FULL_MASK, bg, src); bf = __shfl_sync(FULL_MASK, bf, src);
+        bi = __shfl_sync(FULL_MASK, bi, src); bp = __shfl_sync(FULL_MASK, bp, src);
+        if (w < 0) {  // only NaN gains (or no feature at all): fall back to the first feature, as a sequential scan would
+          bi = F > 0 ? 0 : -1;
+          if (bi == 0) { const SplitKey k0 = V.feat_key[sel * F]; bg = k0.gain; bf = k0.real_feature; bp = k0.pad; }
+        }
       }
       widx[sel] = bi;
       fresh_leaf[sel] = leaf;
@@ -598,14 +634,13 @@ __device__ void find_control(const DevView& V, int mode, bool active, int smalle
     if (l < nl) consider(l, lk[k]);
   }
   for (int l = lane + 32 * CTRL_MAX_LEAF_KEYS; l < nl; l += 32) consider(l, V.leaf_key[l]);
-  for (int o = 16; o > 0; o >>= 1) {
-    const double g2 = __shfl_xor_sync(FULL_MASK, bg, o);
-    const int f2 = __shfl_xor_sync(FULL_MASK, bf, o);
-    const int l2 = __shfl_xor_sync(FULL_MASK, bl, o);
-    const int p2 = __shfl_xor_sync(FULL_MASK, bp, o);
-    if (l2 >= 0) {
-      if (bl < 0 || split_better(g2, f2, bg, bf) || (g2 == bg && f2 == bf && l2 < bl)) { bg = g2; bf = f2; bl = l2; bp = p2; }
-    }
+  {  // first leaf with the best (gain, feature)
+    const unsigned tie = bf == -1 ? 0x7fffffffu : (unsigned)bf;
+    const int w = warp_argmax(bg, tie, (unsigned)bl, bl >= 0 && bg == bg);
+    const int src = w < 0 ? 0 : w;
+    bg = __shfl_sync(FULL_MASK, bg, src); bf = __shfl_sync(FULL_MASK, bf, src);
+    bl = __shfl_sync(FULL_MASK, bl, src); bp = __shfl_sync(FULL_MASK, bp, src);
+    if (w < 0) bl = -1;
   }
   if (lane == 0) {
     if (bl < 0 || !(bg > 0.0)) {
