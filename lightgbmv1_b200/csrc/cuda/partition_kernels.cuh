@@ -278,8 +278,16 @@ __global__ void __launch_bounds__(PART_THREADS) k_part_scatter(DevView V, int un
 //     right side starts), then scatters its rows; the control block runs part_control meanwhile.
 // The arrive/depart counters reset themselves: the last block to leave the barrier zeroes both.
 #define PART_SMEM_TILES 8
+#ifdef LGBCU_STAGE_TIMERS
+#define PSTAGE(i) do { if (blockIdx.x == 0 && threadIdx.x == 0) { long long t_ = clock64(); g_stage_cycles[8 + (i)] += (unsigned long long)(t_ - pt_); pt_ = t_; } } while (0)
+#else
+#define PSTAGE(i) do {} while (0)
+#endif
 __global__ void __launch_bounds__(PART_THREADS) k_partition(DevView V, int mode) {
   DevCtl* c = V.ctl;
+#ifdef LGBCU_STAGE_TIMERS
+  long long pt_ = clock64();
+#endif
   if (c->done) return;
   STAMP(c, 2);
   const int leaf = c->split_leaf;
@@ -300,6 +308,7 @@ __global__ void __launch_bounds__(PART_THREADS) k_partition(DevView V, int mode)
   const int* src = V.indices[L.buf] + L.begin;
   int* dst = V.indices[L.buf ^ 1] + L.begin;
   int row0[PART_REPS];  // rows of the block's first tile stay in registers for the scatter
+  PSTAGE(0);
   if (!control) {
     const DevFeat F = V.feats[c->split_feature];
     const SplitRule rule = make_rule(F, c->split_threshold, c->split_default_left);
@@ -328,6 +337,7 @@ __global__ void __launch_bounds__(PART_THREADS) k_partition(DevView V, int mode)
     }
     if (lane == 0) s_cnt[warp] = lefts;
     __syncthreads();
+    PSTAGE(1);
     if (tid == 0) {
       int t = 0;
       for (int w = 0; w < PART_THREADS / 32; ++w) t += s_cnt[w];
@@ -341,6 +351,7 @@ __global__ void __launch_bounds__(PART_THREADS) k_partition(DevView V, int mode)
     __threadfence();
   }
   __syncthreads();
+  PSTAGE(2);
   // offsets: lefts of the blocks before this one, and of all blocks
   int before = 0, total = 0;
   for (int b = tid; b < P; b += PART_THREADS) {
@@ -357,6 +368,7 @@ __global__ void __launch_bounds__(PART_THREADS) k_partition(DevView V, int mode)
   before = 0; total = 0;
 #pragma unroll
   for (int w = 0; w < PART_THREADS / 32; ++w) { before += s_red[0][w]; total += s_red[1][w]; }
+  PSTAGE(3);
   if (tid == 0) {  // leave the barrier; the last one out re-arms it
     const unsigned d = atomicAdd(&c->bar_depart, 1u);
     if (d == (unsigned)P) { c->bar_arrive = 0; c->bar_depart = 0; }
@@ -404,5 +416,6 @@ __global__ void __launch_bounds__(PART_THREADS) k_partition(DevView V, int mode)
     }
     tile_off += tile_total;
   }
+  PSTAGE(4);
   STAMP_END(split_, 2);
 }
