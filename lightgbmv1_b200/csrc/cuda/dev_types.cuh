@@ -94,7 +94,7 @@ struct DevView {
   int8_t* splittable;        // [num_leaves slots][num_features]  FeatureHistogram::is_splittable_
   int8_t* parent_split;      // [num_features] the split leaf's flags, snapshotted by k_part_scan for both children
   double2* mfb_fix;          // [num_leaves slots][num_features] FixHistogram'd most-frequent-bin entry, in double
-  float* grad; float* hess;
+  const float2* gh;          // interleaved (gradient, hessian) of the current iteration, written by k_absmax
   int* indices[2];
   HistEntry* pool;           // [num_leaves][total_bin]
   DevLeaf* leaves;

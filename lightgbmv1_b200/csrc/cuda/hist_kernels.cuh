@@ -64,7 +64,8 @@ __device__ void hist_global_path(const DevView& V, const DevLeaf& L, bool identi
     const int ck = (int)(p - (long long)pos * nchunk);
     const int row = identity ? pos : idx[pos];
     const uint4 q = *reinterpret_cast<const uint4*>(V.bins + (size_t)row * V.row_stride + ck * 16);
-    const i64 gq = to_fixed(V.grad[row], sg), hq = to_fixed(V.hess[row], sh);
+    const float2 gh = V.gh[row];
+    const i64 gq = to_fixed(gh.x, sg), hq = to_fixed(gh.y, sh);
     const unsigned w[4] = {q.x, q.y, q.z, q.w};
 #pragma unroll
     for (int k = 0; k < 16; ++k) {
@@ -128,7 +129,7 @@ __device__ void hist_shared_path(const DevView& V, const DevLeaf& L, bool identi
       if (pos < b1) {
         const int row = identity ? pos : idx[pos];
         nq = *reinterpret_cast<const uint4*>(colbase + (size_t)row * V.row_stride);
-        ng = V.grad[row]; nh = V.hess[row];
+        { const float2 gh = V.gh[row]; ng = gh.x; nh = gh.y; }
       }
     }
     for (; base < b1; base += HIST_WARPS * 32) {
@@ -141,7 +142,7 @@ __device__ void hist_shared_path(const DevView& V, const DevLeaf& L, bool identi
         if (pos < b1) {
           const int row = identity ? pos : idx[pos];
           nq = *reinterpret_cast<const uint4*>(colbase + (size_t)row * V.row_stride);
-          ng = V.grad[row]; nh = V.hess[row];
+          { const float2 gh = V.gh[row]; ng = gh.x; nh = gh.y; }
         }
       }
       __syncwarp();

@@ -78,6 +78,7 @@ struct LgbCuContext {
   std::vector<DevFeat> h_feats;
   int8_t* d_feat_used = nullptr;
   // per-row state
+  float2* d_gh = nullptr;
   float *d_grad = nullptr, *d_hess = nullptr, *d_label = nullptr, *d_weight = nullptr;
   bool has_weight = false, has_label = false;
   double* d_score = nullptr;
@@ -132,7 +133,7 @@ struct LgbCuContext {
     V.num_data = N; V.num_features = F; V.row_stride = stride; V.total_bin = total_bin; V.num_tiles16 = ntiles16;
     V.bins = d_bins; V.feats = d_feats; V.feat_used = d_feat_used; V.splittable = d_splittable;
     V.parent_split = d_parent_split; V.mfb_fix = d_mfb_fix;
-    V.grad = d_grad; V.hess = d_hess; V.indices[0] = d_indices[0]; V.indices[1] = d_indices[1];
+    V.gh = d_gh; V.indices[0] = d_indices[0]; V.indices[1] = d_indices[1];
     V.pool = d_pool; V.leaves = d_leaves; V.best = d_best; V.feat_best = d_feat_best; V.feat_key = d_feat_key; V.leaf_key = d_leaf_key; V.ctl = d_ctl;
     V.records = d_records; V.tile_left = d_tile_left; V.part_bits = d_part_bits; V.p = params;
     V.data_parallel = (comm != nullptr || force_dp_counts) ? 1 : 0;
@@ -299,7 +300,7 @@ int lgbcu_destroy(LgbCuContext* c) {
   cudaStreamSynchronize(c->stream);
   drop_graph(c);
   lgbcu_comm_destroy(c);
-  void* ptrs[] = {c->d_bins, c->d_feats, c->d_feat_used, c->d_grad, c->d_hess, c->d_label, c->d_weight, c->d_score,
+  void* ptrs[] = {c->d_bins, c->d_feats, c->d_feat_used, c->d_grad, c->d_hess, c->d_gh, c->d_label, c->d_weight, c->d_score,
                   c->d_indices[0], c->d_indices[1], c->d_part_bits, c->d_tile_left, c->d_query, c->d_label_gain,
                   c->d_inv_max_dcg, c->d_sigmoid_table, c->d_pool, c->d_splittable, c->d_leaves, c->d_best,
                   c->d_feat_best, c->d_ctl, c->d_records, c->d_leaf_value, c->d_export, c->d_tree_i32, c->d_tree_i8,
@@ -356,6 +357,7 @@ static int setup_dataset_common(LgbCuContext* c, int32_t num_data, int32_t num_f
   CU(cudaMemsetAsync(c->d_parent_split, 1, num_features, c->stream));
   CU(dev_alloc(&c->d_grad, (size_t)num_data));
   CU(dev_alloc(&c->d_hess, (size_t)num_data));
+  CU(dev_alloc(&c->d_gh, (size_t)num_data));
   CU(dev_alloc(&c->d_score, (size_t)num_data));
   CU(cudaMemsetAsync(c->d_score, 0, sizeof(double) * num_data, c->stream));
   CU(dev_alloc(&c->d_indices[0], (size_t)num_data));
@@ -677,7 +679,7 @@ int lgbcu_begin_tree(LgbCuContext* c, const int32_t* bag_indices, int32_t bag_co
   }
   CU(cudaMemsetAsync(c->d_pool, 0, sizeof(HistEntry) * (size_t)c->params.num_leaves * c->total_bin, c->stream));
   LAUNCH(k_reset_ctl_max, 1, 1, 0, c->stream, c->d_ctl, c->root_count, c->N);
-  LAUNCH(k_absmax, grid_for(c, c->N, 256), 256, 0, c->stream, c->N, c->d_grad, c->d_hess, c->d_ctl);
+  LAUNCH(k_absmax, grid_for(c, c->N, 256), 256, 0, c->stream, c->N, c->d_grad, c->d_hess, c->d_gh, c->d_ctl);
   if (comm_allreduce_tree_setup(c)) return -1;
   LAUNCH(k_prepare_tree, 1, 256, 0, c->stream, c->view(), c->root_count, identity);
   CU(cudaGetLastError());

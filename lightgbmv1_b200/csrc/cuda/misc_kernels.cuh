@@ -38,11 +38,16 @@ __global__ void k_grad_l2(int n, const double* __restrict__ score, const float* 
 }
 
 // max |g|, max |h| as float bit patterns (non-negative floats order like unsigned ints)
-__global__ void k_absmax(int n, const float* __restrict__ grad, const float* __restrict__ hess, DevCtl* ctl) {
+// Also writes the interleaved (g, h) copy the histogram kernel gathers from: one 8-byte load per indexed row
+// instead of two 4-byte loads in two different sectors.
+__global__ void k_absmax(int n, const float* __restrict__ grad, const float* __restrict__ hess, float2* __restrict__ gh,
+                         DevCtl* ctl) {
   unsigned mg = 0, mh = 0;
   for (int i = blockIdx.x * blockDim.x + threadIdx.x; i < n; i += gridDim.x * blockDim.x) {
-    mg = max(mg, __float_as_uint(fabsf(grad[i])));
-    mh = max(mh, __float_as_uint(fabsf(hess[i])));
+    const float g = grad[i], h = hess[i];
+    gh[i] = make_float2(g, h);
+    mg = max(mg, __float_as_uint(fabsf(g)));
+    mh = max(mh, __float_as_uint(fabsf(h)));
   }
   for (int o = 16; o > 0; o >>= 1) {
     mg = max(mg, __shfl_xor_sync(0xffffffffu, mg, o));
