@@ -23,8 +23,10 @@
 //                    against 12.3 for the former warp-private LDS/IADD/STS design (3 warps fit).  The
 //                    sub-histogram is flushed once per block with REDG.ADD.64 (zero entries skipped).
 #pragma once
+#include <cooperative_groups.h>
 #include "dev_types.cuh"
 
+#define HIST_CLUSTER 4                            /* blocks per thread-block cluster: they reduce their sub-histograms through DSMEM */
 #define HIST_THREADS 512                          /* block size of the histogram kernel: 16 warps */
 #define HIST_WARPS (HIST_THREADS / 32)
 #define HIST_BLOCKS_PER_SM 2                      /* 2 x 80 KB of shared memory, 32 resident warps per SM */
@@ -34,6 +36,13 @@
 #define HIST_SMEM_BYTES (HIST_SUB_BYTES + HIST_WARPS * HIST_STAGE_BYTES)
 #define HIST_SMALL_LEAF_ROWS 256
 #define HIST_MIN_ROWS_PER_WARP 16                 /* rows a warp should at least get before another block is recruited */
+
+#ifdef LGBCU_STAGE_TIMERS
+__device__ unsigned long long g_hist_cycles[8];
+#define HSTAGE(i) do { if (blockIdx.x == 0 && threadIdx.x == 0) { long long t_ = clock64(); g_hist_cycles[i] += (unsigned long long)(t_ - ht_); ht_ = t_; } } while (0)
+#else
+#define HSTAGE(i) do {} while (0)
+#endif
 
 __device__ __forceinline__ i64 to_fixed(float v, double scale) {
   return __double2ll_rn((double)v * scale);
@@ -97,21 +106,48 @@ __device__ void hist_shared_path(const DevView& V, const DevLeaf& L, bool identi
   const longlong2* sv2 = reinterpret_cast<const longlong2*>(stage + 512 + ch * 256);
 
   const int NT = V.num_tiles16;
-  // block-level work items: (tile, part); a block's rows are dealt to its warps in batches of 32
-  int PB = (L.count + HIST_WARPS * min_rows - 1) / (HIST_WARPS * min_rows);
-  int cap = nblocks / NT; if (cap < 1) cap = 1;
-  if (PB > cap) PB = cap;
-  if (PB < 1) PB = 1;
-  int per_block = (L.count + PB - 1) / PB;
+  // Work units: (tile, group of HIST_CLUSTER row slices), dealt round-robin to the clusters; the blocks of a cluster
+  // take the HIST_CLUSTER slices of one unit, so that their sub-histograms cover the same tile and can be summed
+  // through distributed shared memory before anything goes to global memory.
+  namespace cg = cooperative_groups;
+  cg::cluster_group cluster = cg::this_cluster();
+  const int rank = (int)cluster.block_rank();
+  const int nclusters = nblocks / HIST_CLUSTER, cluster_id = bid / HIST_CLUSTER;
+  int PG = (L.count + HIST_CLUSTER * HIST_WARPS * min_rows - 1) / (HIST_CLUSTER * HIST_WARPS * min_rows);
+  int cap = nclusters / NT; if (cap < 1) cap = 1;
+  if (PG > cap) PG = cap;
+  if (PG < 1) PG = 1;
+  int per_block = (L.count + PG * HIST_CLUSTER - 1) / (PG * HIST_CLUSTER);
   per_block = (per_block + 31) / 32 * 32;
 
   const int* idx = V.indices[L.buf] + L.begin;
   HistEntry* out = V.pool + (size_t)L.slot * V.total_bin;
 
-  for (int item = bid; item < NT * PB; item += nblocks) {
-    const int tile = item / PB, part = item - tile * PB;
-    const int b0 = part * per_block;
+#ifdef LGBCU_STAGE_TIMERS
+  long long ht_ = clock64();
+#endif
+  for (int unit = cluster_id; unit < NT * PG; unit += nclusters) {
+    const int tile = unit / PG, part = (unit - tile * PG) * HIST_CLUSTER + rank;
+    int b0 = part * per_block; if (b0 > L.count) b0 = L.count;
     int b1 = b0 + per_block; if (b1 > L.count) b1 = L.count;
+    const uint8_t* colbase = V.bins + tile * 16;
+    // software pipeline, two deep: while batch k is accumulated the row data of batch k+1 and the row index of
+    // batch k+2 are in flight; the first loads are issued before the sub-histogram is zeroed
+    const int step = HIST_WARPS * 32;
+    uint4 nq = make_uint4(0, 0, 0, 0);
+    float ng = 0.f, nh = 0.f;
+    int prow = -1;
+    int base = b0 + warp * 32;
+    {
+      const int pos = base + lane;
+      if (pos < b1) {
+        const int row = identity ? pos : idx[pos];
+        nq = *reinterpret_cast<const uint4*>(colbase + (size_t)row * V.row_stride);
+        { const float2 gh = V.gh[row]; ng = gh.x; nh = gh.y; }
+      }
+      const int pos1 = pos + step;
+      if (pos1 < b1) prow = identity ? pos1 : idx[pos1];
+    }
     {
       uint4* z = reinterpret_cast<uint4*>(smem);
       const uint4 zero = make_uint4(0, 0, 0, 0);
@@ -119,31 +155,20 @@ __device__ void hist_shared_path(const DevView& V, const DevLeaf& L, bool identi
       for (int i = tid; i < HIST_SUB_BYTES / 16; i += HIST_THREADS) z[i] = zero;
     }
     __syncthreads();
-    const uint8_t* colbase = V.bins + tile * 16;
-    // software pipeline: the (index ->) row loads of batch k+1 are in flight while batch k is accumulated
-    uint4 nq = make_uint4(0, 0, 0, 0);
-    float ng = 0.f, nh = 0.f;
-    int base = b0 + warp * 32;
-    if (base < b1) {
-      const int pos = base + lane;
-      if (pos < b1) {
-        const int row = identity ? pos : idx[pos];
-        nq = *reinterpret_cast<const uint4*>(colbase + (size_t)row * V.row_stride);
-        { const float2 gh = V.gh[row]; ng = gh.x; nh = gh.y; }
-      }
-    }
-    for (; base < b1; base += HIST_WARPS * 32) {
+    HSTAGE(0);
+    for (; base < b1; base += step) {
       sbins[lane] = nq;
       svals[lane] = to_fixed(ng, sg);
       svals[32 + lane] = to_fixed(nh, sh);
       nq = make_uint4(0, 0, 0, 0); ng = 0.f; nh = 0.f;
+      if (prow >= 0) {
+        nq = *reinterpret_cast<const uint4*>(colbase + (size_t)prow * V.row_stride);
+        { const float2 gh = V.gh[prow]; ng = gh.x; nh = gh.y; }
+      }
       {
-        const int pos = base + HIST_WARPS * 32 + lane;
-        if (pos < b1) {
-          const int row = identity ? pos : idx[pos];
-          nq = *reinterpret_cast<const uint4*>(colbase + (size_t)row * V.row_stride);
-          { const float2 gh = V.gh[row]; ng = gh.x; nh = gh.y; }
-        }
+        const int pos2 = base + 2 * step + lane;
+        prow = -1;
+        if (pos2 < b1) prow = identity ? pos2 : idx[pos2];
       }
       __syncwarp();
       int n = b1 - base; if (n > 32) n = 32;
@@ -173,21 +198,39 @@ __device__ void hist_shared_path(const DevView& V, const DevLeaf& L, bool identi
       }
       __syncwarp();
     }
-    __syncthreads();
-    // flush: thread tid owns column (tid & 31) of bin rows tid>>5, +16, ...
+    // Reduce across the cluster, then flush: block `rank` owns bin rows [rank*32, rank*32+32) of the tile, sums
+    // that slice over the HIST_CLUSTER sub-histograms (its own and the peers', read through DSMEM) and issues one
+    // REDG.ADD.64 per non-zero entry -- 1/HIST_CLUSTER of the global atomics a per-block flush would need.
+    HSTAGE(1);
+    cluster.sync();
+    HSTAGE(2);
     {
       const int f = tile * 16 + fl;
+      int nslots = 0; i64* dst = nullptr;
       if (f < V.num_features) {
         const DevFeat F = V.feats[f];
-        i64* dst = reinterpret_cast<i64*>(out + F.hist_base) + ch;
-        for (int b = warp; b < F.nslots; b += HIST_WARPS) {
-          const int e = b * 32 + lane;
-          const i64 v = (i64)(((unsigned long long)hi[e] << 32) | lo[e]);
-          if (v) atomic_add_i64(dst + 2 * b, v);
-        }
+        nslots = F.nslots;
+        dst = reinterpret_cast<i64*>(out + F.hist_base) + ch;
+      }
+      const unsigned* rlo[HIST_CLUSTER];
+#pragma unroll
+      for (int k = 0; k < HIST_CLUSTER; ++k) rlo[k] = cluster.map_shared_rank(lo, k);
+#pragma unroll
+      for (int rep = 0; rep < (HIST_ROWS_SMEM / HIST_CLUSTER) * 32 / HIST_THREADS; ++rep) {
+        const int e = rank * (HIST_ROWS_SMEM / HIST_CLUSTER) * 32 + rep * HIST_THREADS + tid;  // column = tid & 31
+        const int b = e >> 5;
+        unsigned l[HIST_CLUSTER], h[HIST_CLUSTER];
+#pragma unroll
+        for (int k = 0; k < HIST_CLUSTER; ++k) { l[k] = rlo[k][e]; h[k] = rlo[k][e + HIST_ROWS_SMEM * 32]; }
+        i64 v = 0;
+#pragma unroll
+        for (int k = 0; k < HIST_CLUSTER; ++k) v += (i64)(((unsigned long long)h[k] << 32) | l[k]);
+        if (b < nslots && v) atomic_add_i64(dst + 2 * b, v);
       }
     }
-    __syncthreads();
+    HSTAGE(3);
+    cluster.sync();  // peers may still be reading this block's sub-histogram
+    HSTAGE(4);
   }
 }
 
@@ -205,7 +248,7 @@ __device__ void hist_phase(const DevView& V, int leaf, int mode, int min_rows, i
   }
 }
 
-__global__ void __launch_bounds__(HIST_THREADS, HIST_BLOCKS_PER_SM) k_hist(DevView V, int leaf_arg, int mode, int min_rows, int small_rows) {
+__global__ void __cluster_dims__(HIST_CLUSTER, 1, 1) __launch_bounds__(HIST_THREADS, HIST_BLOCKS_PER_SM) k_hist(DevView V, int leaf_arg, int mode, int min_rows, int small_rows) {
   extern __shared__ __align__(16) unsigned char hist_smem[];
   int leaf;
   STAMP(V.ctl, 0);

@@ -118,6 +118,7 @@ struct LgbCuContext {
   int hist_mode = LGBCU_HIST_AUTO;
   int hist_min_rows = HIST_MIN_ROWS_PER_WARP;
   int hist_small_rows = HIST_SMALL_LEAF_ROWS;
+  int hist_grid = 0;  // clusters that can be resident at once x HIST_CLUSTER
   bool force_dp_counts = false;  // LGBCU_FORCE_DP_COUNTS=1: single rank, but leaf counts as in data-parallel mode (tests)
   cudaGraphExec_t tree_graph = nullptr; bool use_graph = true;  // the per-tree launch sequence, captured once
   int objective = LGBCU_OBJ_NONE; double obj_p[3] = {0, 0, 0};
@@ -180,7 +181,7 @@ int ensure_tree_buffers(LgbCuContext* c) {
 
 int launch_hist(LgbCuContext* c, int leaf_arg) {
   const DevView V = c->view();
-  LAUNCH(k_hist, c->num_sms * HIST_BLOCKS_PER_SM, HIST_THREADS, HIST_SMEM_BYTES, c->stream, V, leaf_arg, c->hist_mode, c->hist_min_rows, c->hist_small_rows);
+  LAUNCH(k_hist, c->hist_grid, HIST_THREADS, HIST_SMEM_BYTES, c->stream, V, leaf_arg, c->hist_mode, c->hist_min_rows, c->hist_small_rows);
   CU(cudaGetLastError());
   return 0;
 }
@@ -283,6 +284,25 @@ int lgbcu_create(int device_id, LgbCuContext** out) {
   CU(cudaMallocHost(reinterpret_cast<void**>(&c->h_leaf), sizeof(DevLeaf)));
   CU(cudaMallocHost(reinterpret_cast<void**>(&c->h_split), sizeof(DevSplit)));
   CU(cudaFuncSetAttribute(k_hist, cudaFuncAttributeMaxDynamicSharedMemorySize, HIST_SMEM_BYTES));
+  {
+    // the histogram kernel is persistent over its work units: as many clusters as the GPU can hold at once
+    cudaLaunchConfig_t cfg = {};
+    cfg.gridDim = dim3((unsigned)(c->num_sms * HIST_BLOCKS_PER_SM / HIST_CLUSTER * HIST_CLUSTER));
+    cfg.blockDim = dim3(HIST_THREADS);
+    cfg.dynamicSmemBytes = HIST_SMEM_BYTES;
+    cudaLaunchAttribute at[1];
+    at[0].id = cudaLaunchAttributeClusterDimension;
+    at[0].val.clusterDim.x = HIST_CLUSTER; at[0].val.clusterDim.y = 1; at[0].val.clusterDim.z = 1;
+    cfg.attrs = at; cfg.numAttrs = 1;
+    int nclusters = 0;
+    CU(cudaOccupancyMaxActiveClusters(&nclusters, k_hist, &cfg));
+    NEED(nclusters >= 1, "lgbcu_create: device %d cannot hold one %d-block cluster of the histogram kernel", device_id, HIST_CLUSTER);
+    const int want = c->num_sms * HIST_BLOCKS_PER_SM / HIST_CLUSTER;
+    if (nclusters > want) nclusters = want;
+    if (const char* e = std::getenv("LGBCU_HIST_CLUSTERS")) { const int v = std::atoi(e); if (v >= 1 && v < nclusters) nclusters = v; }
+    c->hist_grid = nclusters * HIST_CLUSTER;
+    if (std::getenv("LGBCU_VERBOSE")) std::fprintf(stderr, "[lgbcu] histogram kernel: %d clusters of %d blocks\n", nclusters, HIST_CLUSTER);
+  }
   {
     int coop = 0;
     CU(cudaDeviceGetAttribute(&coop, cudaDevAttrCooperativeLaunch, device_id));
@@ -923,6 +943,13 @@ extern "C" int lgbcu_debug_stamps(unsigned long long* out, int n) {
   cudaMemcpyFromSymbol(out + n, g_ends, sizeof(unsigned long long) * (size_t)n);
   static unsigned long long z[3 * 4096];
   cudaMemcpyToSymbol(g_ends, z, sizeof(z));
+  return 0;
+}
+extern "C" int lgbcu_debug_hist_stages(unsigned long long* out8, int reset) {
+  unsigned long long z[8] = {0};
+  cudaDeviceSynchronize();
+  cudaMemcpyFromSymbol(out8, g_hist_cycles, sizeof(z));
+  if (reset) cudaMemcpyToSymbol(g_hist_cycles, z, sizeof(z));
   return 0;
 }
 extern "C" int lgbcu_debug_stages(unsigned long long* out16, int reset) {
