@@ -71,10 +71,10 @@ struct DevCtl {
   int kg, kh;        // fixed-point exponents
   double scale_g, scale_h, inv_g, inv_h;
   unsigned feat_done;  // "last block done" counter of k_find_split
-  unsigned bar_arrive;  // inter-block barrier of k_partition (self-resetting)
+  unsigned part_epoch;  // launches of k_partition so far (tags the words of V.part_sync); never reset
+  unsigned bar_arrive, bar_base;  // k_partition: blocks arrived so far (monotonic) / its value when this launch began
   long long global_root;  // root rows over all ranks   } adjacent: one 2 x int64 sum all-reduce
   long long global_rows;  // dataset rows over all ranks }
-  unsigned bar_depart, pad1;
   unsigned long long prof_hist_rows, prof_hist_rows_indexed, prof_hist_calls, prof_hist_ns;
 };
 
@@ -104,7 +104,7 @@ struct DevView {
   SplitKey* leaf_key;        // [num_leaves]      (gain, real feature) of best
   DevCtl* ctl;
   LgbCuSplitRecord* records;
-  int* tile_left;            // partition scratch: lefts per 1024-row tile, then exclusive offsets
+  unsigned long long* part_sync;  // partition scratch: (epoch << 32 | left count) per block
   unsigned* part_bits;       // partition scratch: 1 bit per row (1 = goes left)
   DevParams p;
 };

@@ -85,7 +85,7 @@ struct LgbCuContext {
   int* d_indices[2] = {nullptr, nullptr};
   double* h_stage[2] = {nullptr, nullptr}; cudaEvent_t stage_ev[2] = {nullptr, nullptr};  // D2H staging of lgbcu_copy_score
   unsigned* d_part_bits = nullptr;
-  int* d_tile_left = nullptr;
+  unsigned long long* d_part_sync = nullptr;
   // query structure (lambdarank)
   int* d_query = nullptr; int num_queries = 0; int max_query = 0;
   std::vector<int> h_query;
@@ -136,7 +136,7 @@ struct LgbCuContext {
     V.parent_split = d_parent_split; V.mfb_fix = d_mfb_fix;
     V.gh = d_gh; V.indices[0] = d_indices[0]; V.indices[1] = d_indices[1];
     V.pool = d_pool; V.leaves = d_leaves; V.best = d_best; V.feat_best = d_feat_best; V.feat_key = d_feat_key; V.leaf_key = d_leaf_key; V.ctl = d_ctl;
-    V.records = d_records; V.tile_left = d_tile_left; V.part_bits = d_part_bits; V.p = params;
+    V.records = d_records; V.part_sync = d_part_sync; V.part_bits = d_part_bits; V.p = params;
     V.data_parallel = (comm != nullptr || force_dp_counts) ? 1 : 0;
     return V;
   }
@@ -321,7 +321,7 @@ int lgbcu_destroy(LgbCuContext* c) {
   drop_graph(c);
   lgbcu_comm_destroy(c);
   void* ptrs[] = {c->d_bins, c->d_feats, c->d_feat_used, c->d_grad, c->d_hess, c->d_gh, c->d_label, c->d_weight, c->d_score,
-                  c->d_indices[0], c->d_indices[1], c->d_part_bits, c->d_tile_left, c->d_query, c->d_label_gain,
+                  c->d_indices[0], c->d_indices[1], c->d_part_bits, c->d_part_sync, c->d_query, c->d_label_gain,
                   c->d_inv_max_dcg, c->d_sigmoid_table, c->d_pool, c->d_splittable, c->d_leaves, c->d_best,
                   c->d_feat_best, c->d_ctl, c->d_records, c->d_leaf_value, c->d_export, c->d_tree_i32, c->d_tree_i8,
                   c->d_tree_f64, c->d_rows, c->d_scratch, c->d_parent_split, c->d_mfb_fix, c->d_feat_key, c->d_leaf_key};
@@ -383,7 +383,8 @@ static int setup_dataset_common(LgbCuContext* c, int32_t num_data, int32_t num_f
   CU(dev_alloc(&c->d_indices[0], (size_t)num_data));
   CU(dev_alloc(&c->d_indices[1], (size_t)num_data));
   const size_t ntiles = ((size_t)num_data + PART_TILE - 1) / PART_TILE;
-  CU(dev_alloc(&c->d_tile_left, ntiles + 1));
+  CU(dev_alloc(&c->d_part_sync, (size_t)c->num_sms * 4 + 2));
+  CU(cudaMemset(c->d_part_sync, 0, sizeof(unsigned long long) * ((size_t)c->num_sms * 4 + 2)));
   CU(dev_alloc(&c->d_part_bits, ntiles * (PART_TILE / 32)));
   CU(dev_alloc(&c->d_export, (size_t)2 * c->total_bin));
   c->alloc_leaves = 0;  // pool depends on total_bin

@@ -99,7 +99,7 @@ __global__ void k_prepare_tree(DevView V, int root_count, int root_identity) {
     c->num_leaves = 1; c->done = 0; c->smaller = 0; c->larger = -1;
     c->split_leaf = c->split_feature = c->split_threshold = 0;
     c->split_default_left = 0; c->split_right_leaf = 1; c->split_left_count = 0;
-    c->num_splits = 0; c->feat_done = 0; c->bar_arrive = 0; c->bar_depart = 0;
+    c->num_splits = 0; c->feat_done = 0;
     c->root_identity = root_identity; c->num_data = root_count;
     c->kg = fixed_exponent(c->max_g_bits, scale_rows);
     c->kh = fixed_exponent(c->max_h_bits, scale_rows);

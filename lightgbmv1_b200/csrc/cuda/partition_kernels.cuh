@@ -3,13 +3,10 @@
 // src/io/dense_bin.hpp:173-253 for single-feature groups) and the host bookkeeping that follows it in
 // SerialTreeLearner::SplitInner (serial_tree_learner.cpp:541-659) and BeforeFindBestSplit (:274-314).
 //
-// Stable two-way compaction in three launches, all sized for the worst case and driven by DevCtl:
-//   k_part_flags   : per row, gather the split feature's stored bin, decide left/right, warp-ballot the
-//                    decisions into a bit mask and count lefts per 1024-row tile;
-//   k_part_scan    : one block; exclusive scan of the tile counts, then the control step (leaf table, split
-//                    record, smaller/larger choice, depth / min_data gates);
-//   k_part_scatter : per row, rank = tile offset + popc prefix of the ballot words; write the row index into
-//                    the other ping-pong buffer, lefts first -- order inside each side is preserved.
+// Stable two-way compaction in ONE launch (k_partition, below), driven by DevCtl: per row, gather the split
+// feature's stored bin, decide left/right, warp-ballot the decisions into bit masks, exchange one left-count per
+// block, then write the row index into the other ping-pong buffer, lefts first -- order inside each side is
+// preserved; one extra block does the control step (leaf table, split record, smaller/larger, gates).
 #pragma once
 #include "dev_types.cuh"
 
@@ -61,92 +58,6 @@ __device__ __forceinline__ bool goes_left(const SplitRule& r, int bin) {
   }
   if (r.miss_na && !r.mfb_na) return r.missing_left;
   return r.maxbin_left;
-}
-
-__device__ void part_flags_phase(const DevView& V, int bid, int nblocks) {
-  const DevCtl* c = V.ctl;
-  const DevLeaf L = V.leaves[c->split_leaf];
-  const DevFeat F = V.feats[c->split_feature];
-  const SplitRule rule = make_rule(F, c->split_threshold, c->split_default_left);
-  const int* src = V.indices[L.buf] + L.begin;
-  const uint8_t* col = V.bins + c->split_feature;
-  const int ntiles = (L.count + PART_TILE - 1) / PART_TILE;
-  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
-  __shared__ int s_cnt[PART_THREADS / 32];
-  for (int tile = bid; tile < ntiles; tile += nblocks) {
-    int lefts = 0;
-#pragma unroll
-    for (int r = 0; r < PART_REPS; ++r) {
-      const int pos = tile * PART_TILE + r * PART_THREADS + threadIdx.x;
-      bool left = false;
-      if (pos < L.count) {
-        const int row = src[pos];
-        left = goes_left(rule, col[(size_t)row * V.row_stride]);
-      }
-      const unsigned word = __ballot_sync(0xffffffffu, left);
-      if (lane == 0) {
-        V.part_bits[(size_t)tile * (PART_TILE / 32) + r * (PART_THREADS / 32) + warp] = word;
-        lefts += __popc(word);
-      }
-    }
-    if (lane == 0) s_cnt[warp] = lefts;
-    __syncthreads();
-    if (threadIdx.x == 0) {
-      int t = 0;
-      for (int w = 0; w < PART_THREADS / 32; ++w) t += s_cnt[w];
-      V.tile_left[tile] = t;
-    }
-    __syncthreads();
-  }
-}
-
-__device__ void part_control(const DevView& V, int mode, int leaf, const DevLeaf& L, int left_cnt);
-
-// mode 0: training (control step runs); mode 1: step-wise API (only counts/ranges are updated, sums untouched).
-// One block (any multiple of 32 threads up to 1024).
-__device__ void part_scan_phase(const DevView& V, int mode) {
-  DevCtl* c = V.ctl;
-  const int leaf = c->split_leaf;
-  const DevLeaf L = V.leaves[leaf];
-  const int ntiles = (L.count + PART_TILE - 1) / PART_TILE;
-  if (mode == 0) {  // snapshot FeatureHistogram::is_splittable_ of the leaf being split for k_find_split
-    const int8_t* src = V.splittable + (size_t)L.slot * V.num_features;
-    for (int f = threadIdx.x; f < V.num_features; f += blockDim.x) V.parent_split[f] = src[f];
-  }
-  __shared__ int s_warp[32];
-  __shared__ int s_carry;
-  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
-  if (threadIdx.x == 0) s_carry = 0;
-  __syncthreads();
-  const int nthreads = blockDim.x;
-  for (int base = 0; base < ntiles; base += nthreads) {
-    const int i = base + threadIdx.x;
-    const int v = i < ntiles ? V.tile_left[i] : 0;
-    int inc = v;
-    for (int o = 1; o < 32; o <<= 1) {
-      const int x = __shfl_up_sync(0xffffffffu, inc, o);
-      if (lane >= o) inc += x;
-    }
-    if (lane == 31) s_warp[warp] = inc;
-    __syncthreads();
-    if (warp == 0) {
-      int w = lane < nthreads / 32 ? s_warp[lane] : 0;
-      int winc = w;
-      for (int o = 1; o < 32; o <<= 1) {
-        const int x = __shfl_up_sync(0xffffffffu, winc, o);
-        if (lane >= o) winc += x;
-      }
-      s_warp[lane] = winc - w;  // exclusive prefix of warp sums
-    }
-    __syncthreads();
-    const int excl = s_carry + s_warp[warp] + inc - v;
-    if (i < ntiles) V.tile_left[i] = excl;
-    __syncthreads();
-    if (threadIdx.x == nthreads - 1) s_carry = excl + v;
-    __syncthreads();
-  }
-  if (threadIdx.x != 0) return;
-  part_control(V, mode, leaf, L, s_carry);
 }
 
 // The bookkeeping that follows a partition (one thread): leaf table, split record, smaller/larger, gates.
@@ -209,74 +120,18 @@ __device__ void part_control(const DevView& V, int mode, int leaf, const DevLeaf
   if (c->num_leaves >= V.p.num_leaves) c->done = 2;  // tree is full; nothing more to enqueue
 }
 
-__device__ void part_scatter_phase(const DevView& V, int bid, int nblocks) {
-  const DevCtl* c = V.ctl;
-  const int leaf = c->split_leaf;
-  const DevLeaf A = V.leaves[leaf];  // already the left child: begin unchanged, buf flipped
-  const int left_total = c->split_left_count;
-  const int count = left_total + V.leaves[c->split_right_leaf].count;
-  const int* src = V.indices[A.buf ^ 1] + A.begin;
-  int* dst = V.indices[A.buf] + A.begin;
-  const int ntiles = (count + PART_TILE - 1) / PART_TILE;
-  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
-  for (int tile = bid; tile < ntiles; tile += nblocks) {
-    // every warp redundantly scans the tile's 32 ballot words (no block sync needed)
-    const unsigned myword = V.part_bits[(size_t)tile * (PART_TILE / 32) + lane];
-    const int pc = __popc(myword);
-    int inc = pc;
-    for (int o = 1; o < 32; o <<= 1) {
-      const int x = __shfl_up_sync(0xffffffffu, inc, o);
-      if (lane >= o) inc += x;
-    }
-    const int excl = inc - pc;
-    const int tile_off = V.tile_left[tile];
-#pragma unroll
-    for (int r = 0; r < PART_REPS; ++r) {
-      const int w = r * (PART_THREADS / 32) + warp;
-      const unsigned word = __shfl_sync(0xffffffffu, myword, w);
-      const int wpre = __shfl_sync(0xffffffffu, excl, w);
-      const int pos = tile * PART_TILE + w * 32 + lane;
-      if (pos < count) {
-        const unsigned lt = (1u << lane) - 1u;
-        const int row = src[pos];
-        if ((word >> lane) & 1u) {
-          dst[tile_off + wpre + __popc(word & lt)] = row;
-        } else {
-          const int rights_before = (tile * PART_TILE - tile_off) + (w * 32 - wpre) + __popc(~word & lt);
-          dst[left_total + rights_before] = row;
-        }
-      }
-    }
-  }
-}
-
-// stand-alone launches (step-wise API and the non-persistent training loop)
-__global__ void __launch_bounds__(PART_THREADS) k_part_flags(DevView V) {
-  if (V.ctl->done) return;
-  part_flags_phase(V, blockIdx.x, gridDim.x);
-}
-__global__ void __launch_bounds__(1024) k_part_scan(DevView V, int mode) {
-  if (V.ctl->done) return;
-  part_scan_phase(V, mode);
-}
-__global__ void __launch_bounds__(PART_THREADS) k_part_scatter(DevView V, int unused) {
-  // done == 2 is set by the k_part_scan that just ran for the LAST split: its scatter must still happen
-  if (V.ctl->done == 1) return;
-  (void)unused;
-  part_scatter_phase(V, blockIdx.x, gridDim.x);
-}
-
 // ---------------------------------------------------------------------------------------------------------------
-// Fused partition: flags -> (inter-block barrier) -> scatter + control in ONE launch.  The three-launch version
-// above spends most of its time in launch ramps and dependent control loads for the typical 10^4..10^5-row leaf;
-// here the only inter-block communication is one left-count per block and one arrive counter.
+// Fused partition: flags -> (inter-block exchange) -> scatter + control in ONE launch.
 //   * blocks [0, P) own contiguous chunks of 1024-row tiles; block P (one extra) is the control block;
 //   * phase 1: decisions -> ballot words (shared memory for a block's first PART_SMEM_TILES tiles, V.part_bits
-//     beyond), block left-count -> V.tile_left[block]; arrive;
-//   * barrier: spin until all P blocks have arrived (the launch is cooperative, so co-residency is guaranteed);
-//   * phase 2: every block sums the counts of the blocks before it (its write offset) and of all blocks (where the
-//     right side starts), then scatters its rows; the control block runs part_control meanwhile.
-// The arrive/depart counters reset themselves: the last block to leave the barrier zeroes both.
+//     beyond); the block's left-count is published as ONE 64-bit word (epoch << 32 | count) in V.part_sync[block];
+//   * exchange: a block bumps a (never reset) arrive counter after publishing; one thread per block polls that
+//     counter until all P blocks are in (polling the words themselves from every thread measured slower: the
+//     readers starve the writers), then every block reads the P words once.  Count and "ready" tag travel in the
+//     same word, so no fence is needed: a reader that still finds an old tag spins on that word.  The sums over the
+//     blocks before it / over all blocks give a block its write offset and the start of the right side.  (The
+//     launch is cooperative, so all blocks are resident and the spins cannot deadlock.)
+//   * phase 2: scatter; the control block runs part_control meanwhile and bumps the epoch.
 #define PART_SMEM_TILES 8
 #ifdef LGBCU_STAGE_TIMERS
 #define PSTAGE(i) do { if (blockIdx.x == 0 && threadIdx.x == 0) { long long t_ = clock64(); g_stage_cycles[8 + (i)] += (unsigned long long)(t_ - pt_); pt_ = t_; } } while (0)
@@ -291,6 +146,8 @@ __global__ void __launch_bounds__(PART_THREADS) k_partition(DevView V, int mode)
   if (c->done) return;
   STAMP(c, 2);
   const int leaf = c->split_leaf;
+  const unsigned epoch = c->part_epoch + 1u;  // every block reads these before it publishes; the control block
+  const unsigned bar_base = c->bar_base;      // updates them after all blocks have arrived
   const DevLeaf L = V.leaves[leaf];
   const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
   const int ntiles = (L.count + PART_TILE - 1) / PART_TILE;
@@ -341,24 +198,26 @@ __global__ void __launch_bounds__(PART_THREADS) k_partition(DevView V, int mode)
     if (tid == 0) {
       int t = 0;
       for (int w = 0; w < PART_THREADS / 32; ++w) t += s_cnt[w];
-      __stcg(&V.tile_left[bid], t);
-      __threadfence();
+      *reinterpret_cast<volatile unsigned long long*>(&V.part_sync[bid]) = ((unsigned long long)epoch << 32) | (unsigned)t;
       atomicAdd(&c->bar_arrive, 1u);
     }
   }
+  // one thread per block waits on the arrive counter (light polling); the words are then read once -- should one
+  // not be visible yet (no fence orders it before the counter), its reader spins on the epoch tag
   if (tid == 0) {
-    while (*reinterpret_cast<volatile unsigned*>(&c->bar_arrive) < (unsigned)P) { }
-    __threadfence();
+    while (*reinterpret_cast<volatile unsigned*>(&c->bar_arrive) - bar_base < (unsigned)P) { }
   }
   __syncthreads();
-  PSTAGE(2);
   // offsets: lefts of the blocks before this one, and of all blocks
   int before = 0, total = 0;
   for (int b = tid; b < P; b += PART_THREADS) {
-    const int v = __ldcg(&V.tile_left[b]);
+    unsigned long long w;
+    do { w = *reinterpret_cast<volatile unsigned long long*>(&V.part_sync[b]); } while ((unsigned)(w >> 32) != epoch);
+    const int v = (int)(unsigned)w;
     total += v;
     if (b < bid) before += v;
   }
+  PSTAGE(2);
   for (int o = 16; o > 0; o >>= 1) {
     before += __shfl_xor_sync(0xffffffffu, before, o);
     total += __shfl_xor_sync(0xffffffffu, total, o);
@@ -369,10 +228,6 @@ __global__ void __launch_bounds__(PART_THREADS) k_partition(DevView V, int mode)
 #pragma unroll
   for (int w = 0; w < PART_THREADS / 32; ++w) { before += s_red[0][w]; total += s_red[1][w]; }
   PSTAGE(3);
-  if (tid == 0) {  // leave the barrier; the last one out re-arms it
-    const unsigned d = atomicAdd(&c->bar_depart, 1u);
-    if (d == (unsigned)P) { c->bar_arrive = 0; c->bar_depart = 0; }
-  }
 #ifdef LGBCU_STAGE_TIMERS
   const int split_ = V.ctl->num_splits;  // (racy by one against the control block: good enough for a probe)
 #endif
@@ -381,7 +236,7 @@ __global__ void __launch_bounds__(PART_THREADS) k_partition(DevView V, int mode)
       const int8_t* sp = V.splittable + (size_t)L.slot * V.num_features;
       for (int f = tid; f < V.num_features; f += PART_THREADS) V.parent_split[f] = sp[f];
     }
-    if (tid == 0) part_control(V, mode, leaf, L, total);
+    if (tid == 0) { part_control(V, mode, leaf, L, total); c->part_epoch = epoch; c->bar_base = bar_base + (unsigned)P; }
     return;
   }
   const int left_total = total;
