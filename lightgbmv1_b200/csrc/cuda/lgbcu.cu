@@ -86,6 +86,7 @@ struct LgbCuContext {
   double* h_stage[2] = {nullptr, nullptr}; cudaEvent_t stage_ev[2] = {nullptr, nullptr};  // D2H staging of lgbcu_copy_score
   unsigned* d_part_bits = nullptr;
   unsigned long long* d_part_sync = nullptr;
+  uint8_t* d_bins_col = nullptr; long long col_stride = 0;
   // query structure (lambdarank)
   int* d_query = nullptr; int num_queries = 0; int max_query = 0;
   std::vector<int> h_query;
@@ -118,6 +119,7 @@ struct LgbCuContext {
   int hist_mode = LGBCU_HIST_AUTO;
   int hist_min_rows = HIST_MIN_ROWS_PER_WARP;
   int hist_small_rows = HIST_SMALL_LEAF_ROWS;
+  int part_blocks_per_sm = PART_BLOCKS_PER_SM;  // lowered at create time if fewer k_partition blocks fit on an SM
   int hist_grid = 0;  // clusters that can be resident at once x HIST_CLUSTER
   bool force_dp_counts = false;  // LGBCU_FORCE_DP_COUNTS=1: single rank, but leaf counts as in data-parallel mode (tests)
   cudaGraphExec_t tree_graph = nullptr; bool use_graph = true;  // the per-tree launch sequence, captured once
@@ -136,7 +138,7 @@ struct LgbCuContext {
     V.parent_split = d_parent_split; V.mfb_fix = d_mfb_fix;
     V.gh = d_gh; V.indices[0] = d_indices[0]; V.indices[1] = d_indices[1];
     V.pool = d_pool; V.leaves = d_leaves; V.best = d_best; V.feat_best = d_feat_best; V.feat_key = d_feat_key; V.leaf_key = d_leaf_key; V.ctl = d_ctl;
-    V.records = d_records; V.part_sync = d_part_sync; V.part_bits = d_part_bits; V.p = params;
+    V.records = d_records; V.part_sync = d_part_sync; V.bins_col = d_bins_col; V.col_stride = col_stride; V.part_bits = d_part_bits; V.p = params;
     V.data_parallel = (comm != nullptr || force_dp_counts) ? 1 : 0;
     return V;
   }
@@ -191,7 +193,7 @@ int launch_hist(LgbCuContext* c, int leaf_arg) {
 int launch_partition(LgbCuContext* c, long long rows, int mode) {
   const DevView V = c->view();
   cudaLaunchConfig_t cfg = {};
-  cfg.gridDim = dim3((unsigned)grid_for(c, rows, PART_TILE, 4) + 1u);
+  cfg.gridDim = dim3((unsigned)grid_for(c, rows, PART_TILE, c->part_blocks_per_sm) + 1u);
   cfg.blockDim = dim3(PART_THREADS);
   cfg.dynamicSmemBytes = 0;
   cfg.stream = c->stream;
@@ -307,6 +309,11 @@ int lgbcu_create(int device_id, LgbCuContext** out) {
     int coop = 0;
     CU(cudaDeviceGetAttribute(&coop, cudaDevAttrCooperativeLaunch, device_id));
     NEED(coop != 0, "lgbcu_create: device %d cannot do cooperative launches (needed by the fused partition)", device_id);
+    int per_sm = 0;
+    CU(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, k_partition, PART_THREADS, 0));
+    NEED(per_sm >= 2, "lgbcu_create: only %d k_partition block(s) fit on an SM", per_sm);
+    // one slot per SM is left for the control block
+    if (per_sm - 1 < c->part_blocks_per_sm) c->part_blocks_per_sm = per_sm - 1;
     if (const char* e = std::getenv("LGBCU_GRAPH")) c->use_graph = std::atoi(e) != 0;
     if (const char* e = std::getenv("LGBCU_FORCE_DP_COUNTS")) c->force_dp_counts = std::atoi(e) != 0;
   }
@@ -321,7 +328,7 @@ int lgbcu_destroy(LgbCuContext* c) {
   drop_graph(c);
   lgbcu_comm_destroy(c);
   void* ptrs[] = {c->d_bins, c->d_feats, c->d_feat_used, c->d_grad, c->d_hess, c->d_gh, c->d_label, c->d_weight, c->d_score,
-                  c->d_indices[0], c->d_indices[1], c->d_part_bits, c->d_part_sync, c->d_query, c->d_label_gain,
+                  c->d_indices[0], c->d_indices[1], c->d_part_bits, c->d_part_sync, c->d_bins_col, c->d_query, c->d_label_gain,
                   c->d_inv_max_dcg, c->d_sigmoid_table, c->d_pool, c->d_splittable, c->d_leaves, c->d_best,
                   c->d_feat_best, c->d_ctl, c->d_records, c->d_leaf_value, c->d_export, c->d_tree_i32, c->d_tree_i8,
                   c->d_tree_f64, c->d_rows, c->d_scratch, c->d_parent_split, c->d_mfb_fix, c->d_feat_key, c->d_leaf_key};
@@ -369,6 +376,8 @@ static int setup_dataset_common(LgbCuContext* c, int32_t num_data, int32_t num_f
   CU(dev_alloc(&c->d_feats, (size_t)num_features));
   CU(cudaMemcpyAsync(c->d_feats, c->h_feats.data(), sizeof(DevFeat) * num_features, cudaMemcpyHostToDevice, c->stream));
   CU(dev_alloc(&c->d_bins, (size_t)num_data * c->stride));
+  c->col_stride = ((long long)num_data + 255) / 256 * 256;
+  CU(dev_alloc(&c->d_bins_col, (size_t)c->col_stride * num_features));
   CU(dev_alloc(&c->d_feat_used, (size_t)num_features));
   CU(cudaMemsetAsync(c->d_feat_used, 1, num_features, c->stream));
   CU(dev_alloc(&c->d_feat_best, (size_t)2 * num_features));
@@ -412,6 +421,9 @@ int lgbcu_set_dataset(LgbCuContext* c, int32_t num_data, int32_t num_features, c
     CU(cudaStreamSynchronize(c->stream));
     cudaFree(packed);
   }
+  LAUNCH(k_transpose_bins, grid_for(c, num_data, 256), 256, 0, c->stream, num_data, num_features, c->stride, c->d_bins,
+         c->d_bins_col, c->col_stride);
+  CU(cudaGetLastError());
   CU(cudaStreamSynchronize(c->stream));
   return 0;
 }
@@ -430,6 +442,8 @@ int lgbcu_set_dataset_columns(LgbCuContext* c, int32_t num_data, int32_t num_fea
     CU(cudaMemcpyAsync(t, columns[f], num_data, cudaMemcpyHostToDevice, c->stream));
     LAUNCH(k_scatter_column, grid_for(c, num_data, 256), 256, 0, c->stream, num_data, t, c->d_bins, c->stride, f);
   }
+  LAUNCH(k_transpose_bins, grid_for(c, num_data, 256), 256, 0, c->stream, num_data, num_features, c->stride, c->d_bins,
+         c->d_bins_col, c->col_stride);
   CU(cudaGetLastError());
   CU(cudaStreamSynchronize(c->stream));
   cudaFree(tmp[0]); cudaFree(tmp[1]);

@@ -198,6 +198,24 @@ __global__ void k_scatter_column(int n, const uint8_t* __restrict__ col, uint8_t
   }
 }
 
+// row-major [n][row_stride] -> column-major [F][col_stride] copy (one thread per row: 16-byte loads on the row side,
+// byte stores that are contiguous across the warp on the column side)
+__global__ void k_transpose_bins(int n, int F, int row_stride, const uint8_t* __restrict__ bins, uint8_t* __restrict__ cols,
+                                 long long col_stride) {
+  for (int i = blockIdx.x * blockDim.x + threadIdx.x; i < n; i += gridDim.x * blockDim.x) {
+    const uint4* row = reinterpret_cast<const uint4*>(bins + (size_t)i * row_stride);
+    for (int c16 = 0; c16 * 16 < F; ++c16) {
+      const uint4 q = row[c16];
+      const unsigned w[4] = {q.x, q.y, q.z, q.w};
+#pragma unroll
+      for (int k = 0; k < 16; ++k) {
+        const int f = c16 * 16 + k;
+        if (f < F) cols[(size_t)f * col_stride + i] = (uint8_t)((w[k >> 2] >> ((k & 3) * 8)) & 0xffu);
+      }
+    }
+  }
+}
+
 // Tree::AddPredictionToScore on binned data (src/io/tree.cpp:109-199 with NumericalDecisionInner,
 // include/LightGBM/tree.h:285-300): walk the tree for each listed row (out-of-bag rows, or all rows).
 struct TreeDev {

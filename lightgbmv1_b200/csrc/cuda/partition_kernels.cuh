@@ -133,12 +133,14 @@ __device__ void part_control(const DevView& V, int mode, int leaf, const DevLeaf
 //     launch is cooperative, so all blocks are resident and the spins cannot deadlock.)
 //   * phase 2: scatter; the control block runs part_control meanwhile and bumps the epoch.
 #define PART_SMEM_TILES 8
+#define PART_BLOCKS_PER_SM 4   /* tile-owning blocks per SM (all must be resident: they meet at a barrier) */
+#define PART_COLUMN_FRACTION 16  /* leaves with >= 1/16 of all rows gather from the column-major copy */
 #ifdef LGBCU_STAGE_TIMERS
 #define PSTAGE(i) do { if (blockIdx.x == 0 && threadIdx.x == 0) { long long t_ = clock64(); g_stage_cycles[8 + (i)] += (unsigned long long)(t_ - pt_); pt_ = t_; } } while (0)
 #else
 #define PSTAGE(i) do {} while (0)
 #endif
-__global__ void __launch_bounds__(PART_THREADS) k_partition(DevView V, int mode) {
+__global__ void __launch_bounds__(PART_THREADS, PART_BLOCKS_PER_SM + 1) k_partition(DevView V, int mode) {
   DevCtl* c = V.ctl;
 #ifdef LGBCU_STAGE_TIMERS
   long long pt_ = clock64();
@@ -169,20 +171,39 @@ __global__ void __launch_bounds__(PART_THREADS) k_partition(DevView V, int mode)
   if (!control) {
     const DevFeat F = V.feats[c->split_feature];
     const SplitRule rule = make_rule(F, c->split_threshold, c->split_default_left);
-    const uint8_t* col = V.bins + c->split_feature;
+    // a large leaf holds a sizeable fraction of all rows, in ascending order: the column-major copy then serves many
+    // rows per 32-byte sector; a small leaf touches one sector per row either way and the row-major read leaves
+    // the row in L2 for the histogram pass that follows
+    const bool by_column = (long long)L.count * PART_COLUMN_FRACTION >= V.num_data;
+    const uint8_t* col = by_column ? V.bins_col + (size_t)c->split_feature * V.col_stride : V.bins + c->split_feature;
+    const size_t rstride = by_column ? 1 : (size_t)V.row_stride;
     int lefts = 0;
+    // the row indices of tile k+1 are in flight while the bins of tile k are gathered
+    int nrow[PART_REPS];
+#pragma unroll
+    for (int r = 0; r < PART_REPS; ++r) {
+      const int pos = t0 * PART_TILE + r * PART_THREADS + tid;
+      nrow[r] = pos < L.count ? src[pos] : -1;
+    }
     for (int tile = t0; tile < t1; ++tile) {
       const int lt = tile - t0;
+      int row[PART_REPS];
+#pragma unroll
+      for (int r = 0; r < PART_REPS; ++r) row[r] = nrow[r];
+      if (tile + 1 < t1) {
+#pragma unroll
+        for (int r = 0; r < PART_REPS; ++r) {
+          const int pos = (tile + 1) * PART_TILE + r * PART_THREADS + tid;
+          nrow[r] = pos < L.count ? src[pos] : -1;
+        }
+      }
+      unsigned char bin[PART_REPS];
+#pragma unroll
+      for (int r = 0; r < PART_REPS; ++r) bin[r] = row[r] >= 0 ? col[(size_t)row[r] * rstride] : 0;
 #pragma unroll
       for (int r = 0; r < PART_REPS; ++r) {
-        const int pos = tile * PART_TILE + r * PART_THREADS + tid;
-        bool left = false;
-        int row = 0;
-        if (pos < L.count) {
-          row = src[pos];
-          left = goes_left(rule, col[(size_t)row * V.row_stride]);
-        }
-        if (lt == 0) row0[r] = row;
+        const bool left = row[r] >= 0 && goes_left(rule, bin[r]);
+        if (lt == 0) row0[r] = row[r] >= 0 ? row[r] : 0;
         const unsigned word = __ballot_sync(0xffffffffu, left);
         if (lane == 0) {
           const int wi = r * (PART_THREADS / 32) + warp;
