@@ -195,10 +195,10 @@ __device__ __forceinline__ int key_pack(int feature, int threshold, int default_
 struct ScanSmem {
   double gd[256], hd[256];      // data_[t] as doubles (after FixHistogram)
   i64 gi[256];                  // gradient entries in fixed point (exact prefix / suffix sums)
-  i64 wtot[4][FS_WARPS];        // per-warp totals of the block-wide integer scans / reductions
+  i64 wtot[6][FS_WARPS];        // per-warp totals of the integer scans / reductions (one row per scan)
   double RG[256], RH[256];      // reverse scan: sum_right_gradient / sum_right_hessian after adding bin t
   double LG[256], LH[256];      // forward scan: sum_left_* after adding bin t
-  int cnt[256], RC[256], LC[256];
+  int RC[256], LC[256];
   double base_g, base_h; int base_c;   // forward scan start (implicit first bin of NA features with offset 1)
   Cand wbest[2][FS_WARPS];
   int wsplit[FS_WARPS];
@@ -235,6 +235,39 @@ __device__ __forceinline__ i64 block_scan_i64(i64 v, i64* wtot) {
   return inc + off;
 }
 
+// 128 threads (the upper half of the block) scan 256 elements, two adjacent ones per thread (j = thread index
+// within the group); inclusive prefix (DIR = +1) or suffix (DIR = -1).  One named barrier per call: every call gets
+// its own wtot row.
+#define GROUP_BAR() asm volatile("bar.sync 1, 128;" ::: "memory")
+template <int DIR>
+__device__ __forceinline__ void group_scan_i64(i64 v0, i64 v1, i64* o0, i64* o1, i64* wtot, int j) {
+  const int lane = j & 31, w = j >> 5;
+  const i64 pair = v0 + v1;
+  i64 inc = pair;
+#pragma unroll
+  for (int o = 1; o < 32; o <<= 1) {
+    const i64 x = DIR > 0 ? __shfl_up_sync(FULL_MASK, inc, o) : __shfl_down_sync(FULL_MASK, inc, o);
+    if (DIR > 0 ? lane >= o : lane + o < 32) inc += x;
+  }
+  if (DIR > 0 ? lane == 31 : lane == 0) wtot[w] = inc;
+  GROUP_BAR();
+  i64 off = 0;
+#pragma unroll
+  for (int k = 0; k < FS_WARPS / 2; ++k) if (DIR > 0 ? k < w : k > w) off += wtot[k];
+  const i64 excl = off + inc - pair;  // everything strictly before (DIR > 0) / after (DIR < 0) this thread's pair
+  if (DIR > 0) { *o0 = excl + v0; *o1 = excl + pair; }
+  else { *o1 = excl + v1; *o0 = excl + pair; }
+}
+__device__ __forceinline__ i64 group_sum_i64(i64 v, i64* wtot, int j) {
+  v = warp_sum(v);
+  if ((j & 31) == 0) wtot[j >> 5] = v;
+  GROUP_BAR();
+  i64 t = 0;
+#pragma unroll
+  for (int k = 0; k < FS_WARPS / 2; ++k) t += wtot[k];
+  return t;
+}
+
 // FindBestThreshold for one numerical feature, one block.
 // Arithmetic fidelity.  The reference accumulates bins sequentially in double.  Where its running sums are exactly
 // representable (always for the small / medium leaves where gains tie) a sequential sum equals the exact sum, so
@@ -259,35 +292,16 @@ __device__ void scan_feature_block(ScanSmem& S, int nt, const DevFeat& F, double
   const int t_hi = nt - 1 - (na_missing ? 1 : 0), t_lo = 1 - offset;  // reverse range
   const int t_end = nt - 2;                                            // forward range [0, t_end]
 
-  S.cnt[tid] = (tid < nt) ? round_int(S.hd[tid] * cnt_factor) : 0;
   const int skip_t = skip_default ? (int)F.default_bin - offset : -1000;  // data_ index of the skipped default bin
   const double inv_g = inv_g_in;
-  // gradient sums: exact integer suffix (reverse scan) / prefix (forward scan) sums, one rounding each
-  const bool in_rev = tid >= t_lo && tid <= t_hi && tid != skip_t;
-  const bool in_fwd = two_way && tid <= t_end && tid != skip_t;
-  const i64 my_gi = S.gi[tid];
-  const i64 rev_gi = block_scan_i64<-1>(in_rev ? my_gi : 0, S.wtot[0]);
-  S.RG[tid] = (double)rev_gi * inv_g;
-  if (two_way) {
-    const i64 fwd_gi = block_scan_i64<1>(in_fwd ? my_gi : 0, S.wtot[1]);
-    double base_g = 0.0;
-    if (implicit_first) {
-      const i64 all_g = block_sum_i64(tid < nt ? my_gi : 0, S.wtot[2]);
-      base_g = sum_g - (double)all_g * inv_g;
-    }
-    S.LG[tid] = base_g + (double)fwd_gi * inv_g;
-    if (tid == 0) S.base_g = base_g;
-  }
-  __syncthreads();
-  STAGE(2);
-  // ---- four sequential chains on four warps
-  if (tid == 0) {  // reverse hessian chain (starts from kEpsilon: order matters)
+  // Two things run side by side.  Warps 0 and 1: the two hessian chains (they start from kEpsilon, so the order of
+  // the additions matters) are replayed sequentially by one thread each.  Warps 4..7: everything that is exact in
+  // integers -- gradient sums (64-bit fixed point, rounded once) and the reconstructed counts -- as 128-thread
+  // prefix / suffix scans over the <= 256 bins, two adjacent bins per thread, synchronised on named barrier 1.
+  if (tid == 0) {  // reverse hessian chain
     double ah = LGB_EPS;
     chain1<-1>(S.hd, S.RH, t_hi, t_lo, skip_t, 1.0, &ah);
-  } else if (tid == 32) {  // reverse counts
-    int ac = 0;
-    chain_cnt<-1>(S.cnt, S.RC, t_hi, t_lo, skip_t, 1, &ac);
-  } else if (tid == 64 && two_way) {  // forward hessian chain
+  } else if (tid == 32 && two_way) {  // forward hessian chain
     double lh = LGB_EPS;
     if (implicit_first) {
       lh = sum_h - LGB_EPS;
@@ -295,14 +309,34 @@ __device__ void scan_feature_block(ScanSmem& S, int nt, const DevFeat& F, double
     }
     S.base_h = lh;
     chain1<1>(S.hd, S.LH, 0, t_end, skip_t, 1.0, &lh);
-  } else if (tid == 96 && two_way) {  // forward counts
-    int lc = 0;
-    if (implicit_first) {
-      lc = num_data;
-      chain_cnt<1>(S.cnt, nullptr, 0, nt - 1, -1000, -1, &lc);
+  } else if (warp >= FS_WARPS / 2) {
+    const int j = tid - FS_THREADS / 2;
+    const int e0 = 2 * j, e1 = 2 * j + 1;
+    const i64 g0 = S.gi[e0], g1 = S.gi[e1];
+    const i64 c0 = e0 < nt ? (i64)round_int(S.hd[e0] * cnt_factor) : 0;
+    const i64 c1 = e1 < nt ? (i64)round_int(S.hd[e1] * cnt_factor) : 0;
+    const bool r0 = e0 >= t_lo && e0 <= t_hi && e0 != skip_t, r1 = e1 >= t_lo && e1 <= t_hi && e1 != skip_t;
+    i64 a0, a1;
+    group_scan_i64<-1>(r0 ? g0 : 0, r1 ? g1 : 0, &a0, &a1, S.wtot[0], j);
+    S.RG[e0] = (double)a0 * inv_g; S.RG[e1] = (double)a1 * inv_g;
+    group_scan_i64<-1>(r0 ? c0 : 0, r1 ? c1 : 0, &a0, &a1, S.wtot[1], j);
+    S.RC[e0] = (int)a0; S.RC[e1] = (int)a1;
+    if (two_way) {
+      const bool f0 = e0 <= t_end && e0 != skip_t, f1 = e1 <= t_end && e1 != skip_t;
+      double base_g = 0.0;
+      i64 base_c = 0;
+      if (implicit_first) {
+        const i64 all_g = group_sum_i64((e0 < nt ? g0 : 0) + (e1 < nt ? g1 : 0), S.wtot[2], j);
+        const i64 all_c = group_sum_i64(c0 + c1, S.wtot[3], j);
+        base_g = sum_g - (double)all_g * inv_g;
+        base_c = (i64)num_data - all_c;
+      }
+      group_scan_i64<1>(f0 ? g0 : 0, f1 ? g1 : 0, &a0, &a1, S.wtot[4], j);
+      S.LG[e0] = base_g + (double)a0 * inv_g; S.LG[e1] = base_g + (double)a1 * inv_g;
+      group_scan_i64<1>(f0 ? c0 : 0, f1 ? c1 : 0, &a0, &a1, S.wtot[5], j);
+      S.LC[e0] = (int)(base_c + a0); S.LC[e1] = (int)(base_c + a1);
+      if (j == 0) { S.base_g = base_g; S.base_c = (int)base_c; }
     }
-    S.base_c = lc;
-    chain_cnt<1>(S.cnt, S.LC, 0, t_end, skip_t, 1, &lc);
   }
   __syncthreads();
   STAGE(3);
@@ -549,6 +583,15 @@ __device__ void find_item(const DevView& V, ScanSmem& S, int f, int sel, int sma
 // leaves are copied feat_best -> best word-parallel by lanes 0..19, off the descriptor's critical path.
 #define CTRL_MAX_LEAF_KEYS 8   /* 32 lanes x 8 = 256 leaves prefetched; more are handled by a second pass */
 #define DEVSPLIT_WORDS ((int)(sizeof(DevSplit) / 4))
+// L2 (cache-global) load of a SplitKey another block of this launch has just written: the last-block pattern orders
+// the writers (store, fence, ticket) -- the reader only has to bypass its own, non-coherent L1.
+__device__ __forceinline__ SplitKey load_key_cg(const SplitKey* p) {
+  const int4 v = __ldcg(reinterpret_cast<const int4*>(p));
+  SplitKey k;
+  k.gain = __hiloint2double(v.y, v.x); k.real_feature = v.z; k.pad = v.w;
+  return k;
+}
+
 __device__ void find_control(const DevView& V, int mode, bool active, int smaller, int larger) {
   DevCtl* c = V.ctl;
   const int lane = threadIdx.x & 31;
@@ -564,14 +607,15 @@ __device__ void find_control(const DevView& V, int mode, bool active, int smalle
   }
   SplitKey fresh[2];
   int fresh_leaf[2] = {-1, -1};
+  int widx[2] = {-1, -1};
+  int wcopy[2] = {0, 0};
   if (active) {
-    int widx[2] = {-1, -1};
     SplitKey fk[2];
 #pragma unroll
     for (int sel = 0; sel < 2; ++sel) {  // both key loads are issued before either reduction
       fk[sel].gain = LGB_MIN_SCORE; fk[sel].real_feature = -1; fk[sel].pad = 0;
       const int leaf = sel == 0 ? smaller : larger;
-      if (leaf >= 0 && lane < F) fk[sel] = V.feat_key[sel * F + lane];
+      if (leaf >= 0 && lane < F) fk[sel] = load_key_cg(&V.feat_key[sel * F + lane]);
     }
 #pragma unroll
     for (int sel = 0; sel < 2; ++sel) {
@@ -580,7 +624,7 @@ __device__ void find_control(const DevView& V, int mode, bool active, int smalle
       double bg = LGB_MIN_SCORE; int bf = -1, bi = -1, bp = 0;
       if (lane < F) { bg = fk[sel].gain; bf = fk[sel].real_feature; bp = fk[sel].pad; bi = lane; }
       for (int j = lane + 32; j < F; j += 32) {
-        const SplitKey k = V.feat_key[sel * F + j];
+        const SplitKey k = load_key_cg(&V.feat_key[sel * F + j]);
         if (split_better(k.gain, k.real_feature, bg, bf)) { bg = k.gain; bf = k.real_feature; bp = k.pad; bi = j; }
       }
       {  // (gain, feature) is a total order over distinct features: one winner
@@ -591,7 +635,7 @@ __device__ void find_control(const DevView& V, int mode, bool active, int smalle
         bi = __shfl_sync(FULL_MASK, bi, src); bp = __shfl_sync(FULL_MASK, bp, src);
         if (w < 0) {  // only NaN gains (or no feature at all): fall back to the first feature, as a sequential scan would
           bi = F > 0 ? 0 : -1;
-          if (bi == 0) { const SplitKey k0 = V.feat_key[sel * F]; bg = k0.gain; bf = k0.real_feature; bp = k0.pad; }
+          if (bi == 0) { const SplitKey k0 = load_key_cg(&V.feat_key[sel * F]); bg = k0.gain; bf = k0.real_feature; bp = k0.pad; }
         }
       }
       widx[sel] = bi;
@@ -600,27 +644,28 @@ __device__ void find_control(const DevView& V, int mode, bool active, int smalle
       fresh[sel].real_feature = bi >= 0 ? bf : -1;
       fresh[sel].pad = bi >= 0 ? bp : 0;
     }
-    // best_split_per_leaf_[leaf] = winner: 20 lanes move one 32-bit word each, both loads before both stores
-    {
-      int w[2] = {0, 0};
+    // best_split_per_leaf_[leaf] = winner: 20 lanes move one 32-bit word each; the loads are issued here, the
+    // stores come last so that their latency hides behind the leaf arg-max
 #pragma unroll
-      for (int sel = 0; sel < 2; ++sel)
-        if (fresh_leaf[sel] >= 0 && widx[sel] >= 0 && lane < DEVSPLIT_WORDS)
-          w[sel] = reinterpret_cast<const int*>(V.feat_best + (sel * F + widx[sel]))[lane];
-#pragma unroll
-      for (int sel = 0; sel < 2; ++sel) {
-        if (fresh_leaf[sel] < 0) continue;
-        if (widx[sel] >= 0) {
-          if (lane < DEVSPLIT_WORDS) reinterpret_cast<int*>(V.best + fresh_leaf[sel])[lane] = w[sel];
-        } else if (lane == 0) {
-          DevSplit* r = V.best + fresh_leaf[sel];
-          r->gain = LGB_MIN_SCORE; r->feature = -1; r->real_feature = -1;
-        }
-        if (lane == 0) V.leaf_key[fresh_leaf[sel]] = fresh[sel];
-      }
-    }
+    for (int sel = 0; sel < 2; ++sel)
+      if (fresh_leaf[sel] >= 0 && widx[sel] >= 0 && lane < DEVSPLIT_WORDS)
+        wcopy[sel] = __ldcg(reinterpret_cast<const int*>(V.feat_best + (sel * F + widx[sel])) + lane);
   }
-  if (mode != 0) return;
+  auto finish_copies = [&]() {
+    if (!active) return;
+#pragma unroll
+    for (int sel = 0; sel < 2; ++sel) {
+      if (fresh_leaf[sel] < 0) continue;
+      if (widx[sel] >= 0) {
+        if (lane < DEVSPLIT_WORDS) reinterpret_cast<int*>(V.best + fresh_leaf[sel])[lane] = wcopy[sel];
+      } else if (lane == 0) {
+        DevSplit* r = V.best + fresh_leaf[sel];
+        r->gain = LGB_MIN_SCORE; r->feature = -1; r->real_feature = -1;
+      }
+      if (lane == 0) V.leaf_key[fresh_leaf[sel]] = fresh[sel];
+    }
+  };
+  if (mode != 0) { finish_copies(); return; }
   // ArrayArgs<SplitInfo>::ArgMax(best_split_per_leaf_): first leaf with the best (gain, feature)
   double bg = LGB_MIN_SCORE; int bf = -1, bl = -1, bp = 0;
   auto consider = [&](int l, SplitKey k) {
@@ -653,6 +698,7 @@ __device__ void find_control(const DevView& V, int mode, bool active, int smalle
       c->split_right_leaf = nl;
     }
   }
+  finish_copies();
 }
 
 // mode 0: training (smaller/larger from DevCtl, control step at the end);
@@ -687,7 +733,6 @@ __global__ void __launch_bounds__(FS_THREADS) k_find_split(DevView V, int mode, 
     if (threadIdx.x == 0) g_stage_cycles[6] += (unsigned long long)(clock64() - tc0); g_stage_cycles[7] += 1; return; }
 #endif
   if (!s_last) return;
-  __threadfence();
   if (threadIdx.x >= 32) return;
   if (threadIdx.x == 0) c->feat_done = 0;
   find_control(V, mode, active, smaller, larger);
