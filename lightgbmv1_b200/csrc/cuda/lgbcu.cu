@@ -122,7 +122,7 @@ struct LgbCuContext {
   int part_blocks_per_sm = PART_BLOCKS_PER_SM;  // lowered at create time if fewer k_partition blocks fit on an SM
   int hist_grid = 0;  // clusters that can be resident at once x HIST_CLUSTER
   bool force_dp_counts = false;  // LGBCU_FORCE_DP_COUNTS=1: single rank, but leaf counts as in data-parallel mode (tests)
-  cudaGraphExec_t tree_graph = nullptr; bool use_graph = true;  // the per-tree launch sequence, captured once
+  cudaGraphExec_t tree_graph = nullptr; bool use_graph = true; bool graph_comm = true;  // the per-tree launch sequence, captured once
   int objective = LGBCU_OBJ_NONE; double obj_p[3] = {0, 0, 0};
   int root_count = 0; bool tree_begun = false;
   // profiling
@@ -315,6 +315,7 @@ int lgbcu_create(int device_id, LgbCuContext** out) {
     // one slot per SM is left for the control block
     if (per_sm - 1 < c->part_blocks_per_sm) c->part_blocks_per_sm = per_sm - 1;
     if (const char* e = std::getenv("LGBCU_GRAPH")) c->use_graph = std::atoi(e) != 0;
+    if (const char* e = std::getenv("LGBCU_GRAPH_COMM")) c->graph_comm = std::atoi(e) != 0;
     if (const char* e = std::getenv("LGBCU_FORCE_DP_COUNTS")) c->force_dp_counts = std::atoi(e) != 0;
   }
   *out = c;
@@ -853,7 +854,7 @@ int lgbcu_train_tree(LgbCuContext* c, LgbCuSplitRecord* records, int32_t* num_sp
   const DevView V = c->view();
   const int L = c->params.num_leaves;
   const bool prof = c->profile;
-  if (c->use_graph && !prof && !c->comm) {
+  if (c->use_graph && !prof && (!c->comm || c->graph_comm)) {
     // the launch sequence of a tree is fixed (all sizes are read on the device): capture it once, replay per tree
     if (!c->tree_graph) {
       cudaGraph_t g = nullptr;
@@ -862,6 +863,7 @@ int lgbcu_train_tree(LgbCuContext* c, LgbCuSplitRecord* records, int32_t* num_sp
       bool ok = true;
       for (int s = 0; s < L - 1 && ok; ++s) {
         ok = launch_hist(c, -1) == 0;
+        ok = ok && comm_reduce_hist(c, s) == 0;  // NCCL collectives are capturable: the all-reduce becomes a graph node
         if (s == 0) LAUNCH(k_root_sums, 1, 32, 0, c->stream, V);
         LAUNCH(k_find_split, dim3(c->F, 2), FS_THREADS, 0, c->stream, V, 0, -1);
         ok = ok && launch_partition(c, c->root_count, 0) == 0;

@@ -592,8 +592,16 @@ __device__ __forceinline__ SplitKey load_key_cg(const SplitKey* p) {
   return k;
 }
 
+#ifdef LGBCU_STAGE_TIMERS
+#define CSTAGE(i) do { if (threadIdx.x == 0) { long long t_ = clock64(); g_stage_cycles[11 + (i)] += (unsigned long long)(t_ - ct_); ct_ = t_; } } while (0)
+#else
+#define CSTAGE(i) do {} while (0)
+#endif
 __device__ void find_control(const DevView& V, int mode, bool active, int smaller, int larger) {
   DevCtl* c = V.ctl;
+#ifdef LGBCU_STAGE_TIMERS
+  long long ct_ = clock64();
+#endif
   const int lane = threadIdx.x & 31;
   const int F = V.num_features;
   const int nl = c->num_leaves;
@@ -605,6 +613,7 @@ __device__ void find_control(const DevView& V, int mode, bool active, int smalle
     lk[k].gain = LGB_MIN_SCORE; lk[k].real_feature = -1; lk[k].pad = 0;
     if (mode == 0 && l < nl) lk[k] = V.leaf_key[l];
   }
+  CSTAGE(0);
   SplitKey fresh[2];
   int fresh_leaf[2] = {-1, -1};
   int widx[2] = {-1, -1};
@@ -651,6 +660,7 @@ __device__ void find_control(const DevView& V, int mode, bool active, int smalle
       if (fresh_leaf[sel] >= 0 && widx[sel] >= 0 && lane < DEVSPLIT_WORDS)
         wcopy[sel] = __ldcg(reinterpret_cast<const int*>(V.feat_best + (sel * F + widx[sel])) + lane);
   }
+  CSTAGE(1);
   auto finish_copies = [&]() {
     if (!active) return;
 #pragma unroll
@@ -687,6 +697,7 @@ __device__ void find_control(const DevView& V, int mode, bool active, int smalle
     bl = __shfl_sync(FULL_MASK, bl, src); bp = __shfl_sync(FULL_MASK, bp, src);
     if (w < 0) bl = -1;
   }
+  CSTAGE(2);
   if (lane == 0) {
     if (bl < 0 || !(bg > 0.0)) {
       c->done = 1;  // "No further splits with positive gain"
@@ -699,6 +710,7 @@ __device__ void find_control(const DevView& V, int mode, bool active, int smalle
     }
   }
   finish_copies();
+  CSTAGE(3);
 }
 
 // mode 0: training (smaller/larger from DevCtl, control step at the end);

@@ -23,7 +23,8 @@ for rep in range(3):
     t0 = time.time(); recs = L.train_tree(); dt = time.time() - t0
     lib.lgbcu_debug_stages(out, 0)
     print(f"tree {dt*1e3:.2f} ms; find stages (us per call @1.9GHz): ", [round(out[i] / 1.9e3 / max(1, len(recs)), 2) for i in range(8)],
-          " part stages [ctl+leaf, flags, barrier, prefix, scatter]:", [round(out[8 + i] / 1.9e3 / max(1, len(recs)), 2) for i in range(5)])
+          " part stages [ctl+leaf, flags, barrier, prefix, scatter]:", [round(out[8 + i] / 1.9e3 / max(1, len(recs)), 2) for i in range(3)],
+          " control [prefetch, feature argmax+loads, leaf argmax, writes]:", [round(out[11 + i] / 1.9e3 / max(1, len(recs)), 2) for i in range(4)])
 # per-split start stamps of the three kernels (graph path): deltas = kernel duration + gap
 ns = len(recs)
 st = (ctypes.c_ulonglong * (6 * ns))()
