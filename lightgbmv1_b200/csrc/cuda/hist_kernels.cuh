@@ -127,7 +127,9 @@ __device__ void hist_shared_path(const DevView& V, const DevLeaf& L, bool identi
   long long ht_ = clock64();
 #endif
   for (int unit = cluster_id; unit < NT * PG; unit += nclusters) {
-    const int tile = unit / PG, part = (unit - tile * PG) * HIST_CLUSTER + rank;
+    // tile is the fast index: neighbouring clusters work on the same row slice at the same time, so the second
+    // tile's read of a row (same 32-byte sector) is served by L2 instead of going to DRAM again
+    const int group = unit / NT, tile = unit - group * NT, part = group * HIST_CLUSTER + rank;
     int b0 = part * per_block; if (b0 > L.count) b0 = L.count;
     int b1 = b0 + per_block; if (b1 > L.count) b1 = L.count;
     const uint8_t* colbase = V.bins + tile * 16;
