@@ -597,7 +597,8 @@ __device__ __forceinline__ SplitKey load_key_cg(const SplitKey* p) {
 #else
 #define CSTAGE(i) do {} while (0)
 #endif
-__device__ void find_control(const DevView& V, int mode, bool active, int smaller, int larger) {
+__device__ void find_control(const DevView& V, int mode, bool active, int smaller, int larger,
+                             const SplitKey (*pre_key)[FS_WARPS], const int (*pre_idx)[FS_WARPS]) {
   DevCtl* c = V.ctl;
 #ifdef LGBCU_STAGE_TIMERS
   long long ct_ = clock64();
@@ -624,17 +625,17 @@ __device__ void find_control(const DevView& V, int mode, bool active, int smalle
     for (int sel = 0; sel < 2; ++sel) {  // both key loads are issued before either reduction
       fk[sel].gain = LGB_MIN_SCORE; fk[sel].real_feature = -1; fk[sel].pad = 0;
       const int leaf = sel == 0 ? smaller : larger;
-      if (leaf >= 0 && lane < F) fk[sel] = load_key_cg(&V.feat_key[sel * F + lane]);
+      if (!pre_key && leaf >= 0 && lane < F) fk[sel] = load_key_cg(&V.feat_key[sel * F + lane]);
     }
 #pragma unroll
     for (int sel = 0; sel < 2; ++sel) {
       const int leaf = sel == 0 ? smaller : larger;
       if (leaf < 0) continue;
       double bg = LGB_MIN_SCORE; int bf = -1, bi = -1, bp = 0;
-      if (lane < F) { bg = fk[sel].gain; bf = fk[sel].real_feature; bp = fk[sel].pad; bi = lane; }
-      for (int j = lane + 32; j < F; j += 32) {
-        const SplitKey k = load_key_cg(&V.feat_key[sel * F + j]);
-        if (split_better(k.gain, k.real_feature, bg, bf)) { bg = k.gain; bf = k.real_feature; bp = k.pad; bi = j; }
+      if (pre_key) {  // more than 32 features: the whole block has already reduced them to one candidate per warp
+        if (lane < FS_WARPS) { const SplitKey k = pre_key[sel][lane]; bg = k.gain; bf = k.real_feature; bp = k.pad; bi = pre_idx[sel][lane]; }
+      } else if (lane < F) {
+        bg = fk[sel].gain; bf = fk[sel].real_feature; bp = fk[sel].pad; bi = lane;
       }
       {  // (gain, feature) is a total order over distinct features: one winner
         const unsigned tie = bf == -1 ? 0x7fffffffu : (unsigned)bf;
@@ -717,7 +718,7 @@ __device__ void find_control(const DevView& V, int mode, bool active, int smalle
 // mode 1: explicit single leaf, no control (step-wise API / tests).
 // grid = (num_features, 2): blockIdx.y = 0 scans the smaller leaf, 1 forms larger = parent - smaller and scans it.
 // The last block to finish runs the control step.
-__global__ void __launch_bounds__(FS_THREADS) k_find_split(DevView V, int mode, int leaf_arg) {
+__global__ void __launch_bounds__(FS_THREADS, 4) k_find_split(DevView V, int mode, int leaf_arg) {
   __shared__ ScanSmem S;
   __shared__ int s_last;
   DevCtl* c = V.ctl;
@@ -739,15 +740,55 @@ __global__ void __launch_bounds__(FS_THREADS) k_find_split(DevView V, int mode, 
   __syncthreads();
   STAGE(5);
   STAMP_END(c->num_splits, 1);
+  if (!s_last) return;
+  // More features than one warp covers: all 256 threads reduce the per-feature keys to one candidate per warp
+  // (independent, coalesced loads) before warp 0 runs the control step.
+  __shared__ SplitKey s_pk[2][FS_WARPS];
+  __shared__ int s_pi[2][FS_WARPS];
+  const bool wide = V.num_features > 32;
+  if (wide && active) {
+    const int F = V.num_features, lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+#pragma unroll
+    for (int sel = 0; sel < 2; ++sel) {
+      const int leaf = sel == 0 ? smaller : larger;
+      double bg = LGB_MIN_SCORE; int bf = -1, bi = -1, bp = 0;
+      if (leaf >= 0) {
+        for (int j0 = threadIdx.x; j0 < F; j0 += 4 * FS_THREADS) {
+          SplitKey k[4];
+#pragma unroll
+          for (int u = 0; u < 4; ++u) {
+            const int j = j0 + u * FS_THREADS;
+            k[u].gain = LGB_MIN_SCORE; k[u].real_feature = -1; k[u].pad = 0;
+            if (j < F) k[u] = load_key_cg(&V.feat_key[sel * F + j]);
+          }
+#pragma unroll
+          for (int u = 0; u < 4; ++u) {
+            const int j = j0 + u * FS_THREADS;
+            if (j < F && (bi < 0 || split_better(k[u].gain, k[u].real_feature, bg, bf))) {
+              bg = k[u].gain; bf = k[u].real_feature; bp = k[u].pad; bi = j;
+            }
+          }
+        }
+      }
+      const unsigned tie = bf == -1 ? 0x7fffffffu : (unsigned)bf;
+      int w = warp_argmax(bg, tie, 0u, bi >= 0 && bg == bg);
+      if (w < 0) w = __ffs(__ballot_sync(FULL_MASK, bi >= 0)) - 1;  // only NaN gains in this warp: its first feature
+      if (w < 0) w = 0;
+      const double wg = __shfl_sync(FULL_MASK, bg, w);
+      const int wf = __shfl_sync(FULL_MASK, bf, w), wi = __shfl_sync(FULL_MASK, bi, w), wp = __shfl_sync(FULL_MASK, bp, w);
+      if (lane == 0) { SplitKey k; k.gain = wg; k.real_feature = wf; k.pad = wp; s_pk[sel][warp] = k; s_pi[sel][warp] = wi; }
+    }
+    __syncthreads();
+  }
+  if (threadIdx.x >= 32) return;
 #ifdef LGBCU_STAGE_TIMERS
   long long tc0 = clock64();
-  if (s_last && threadIdx.x < 32) { if (threadIdx.x == 0) c->feat_done = 0; find_control(V, mode, active, smaller, larger);
-    if (threadIdx.x == 0) g_stage_cycles[6] += (unsigned long long)(clock64() - tc0); g_stage_cycles[7] += 1; return; }
 #endif
-  if (!s_last) return;
-  if (threadIdx.x >= 32) return;
   if (threadIdx.x == 0) c->feat_done = 0;
-  find_control(V, mode, active, smaller, larger);
+  find_control(V, mode, active, smaller, larger, wide && active ? s_pk : nullptr, s_pi);
+#ifdef LGBCU_STAGE_TIMERS
+  if (threadIdx.x == 0) { g_stage_cycles[6] += (unsigned long long)(clock64() - tc0); g_stage_cycles[7] += 1; }
+#endif
 }
 
 // Root LeafSplits::Init (leaf_splits.hpp:66-79; all-reduced over ranks in data_parallel_tree_learner.cpp:126-151):

@@ -3,7 +3,9 @@ import sys, os, ctypes, time
 sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
 import numpy as np
 from lightgbmv1_b200 import _native as N
-n, F, leaves = 10_500_000, 28, 255
+n = int(sys.argv[1]) if len(sys.argv) > 1 else 10_500_000
+F = int(sys.argv[2]) if len(sys.argv) > 2 else 28
+leaves = 255
 rng = np.random.default_rng(0)
 metas = [(3,0,0,0) if f % 9 == 8 else ((130,0,0,0) if f % 7 == 6 else (255,127,127,0)) for f in range(F)]
 bins = np.empty((n, F), dtype=np.uint8)
