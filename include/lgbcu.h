@@ -229,6 +229,37 @@ LGBCU_API int lgbcu_partition_rows_noalloc(const uint8_t* bins_dev, int64_t row_
                                            const int32_t* indices_in_dev, int32_t n, int32_t* indices_out_dev,
                                            int32_t* left_count_dev, void* stream);
 
+/* ---- validation sets and evaluation metrics on the device --------------------------------
+ * A validation set is a second binned matrix whose bins come from the TRAINING set's mappers (the reference refuses
+ * anything else: GBDT::AddValidDataset -> Dataset::CheckAlign, src/boosting/gbdt.cpp:121-125); it owns a score vector
+ * (ScoreUpdater, src/boosting/score_updater.hpp:21-125) that every new tree is added to by walking the tree on the
+ * bins (Tree::AddPredictionToScore, src/io/tree.cpp:109-199). `set` = -1 names the training rows. */
+LGBCU_API int lgbcu_valid_create(LgbCuContext* ctx, int32_t num_data, const uint8_t* bins_row_major, int32_t* out_set);
+LGBCU_API int lgbcu_valid_set_label(LgbCuContext* ctx, int32_t set, const float* label, int32_t n);
+LGBCU_API int lgbcu_valid_set_weight(LgbCuContext* ctx, int32_t set, const float* weight, int32_t n);
+LGBCU_API int lgbcu_valid_set_query(LgbCuContext* ctx, int32_t set, const int32_t* boundaries, int32_t num_queries);
+LGBCU_API int lgbcu_valid_set_score(LgbCuContext* ctx, int32_t set, const double* score, int32_t n);
+LGBCU_API int lgbcu_valid_add_const(LgbCuContext* ctx, int32_t set, double value);
+LGBCU_API int lgbcu_valid_add_tree(LgbCuContext* ctx, int32_t set, int32_t num_leaves, const int32_t* split_feature_inner,
+                                   const int32_t* threshold_bin, const int8_t* decision_type, const int32_t* left_child,
+                                   const int32_t* right_child, const double* leaf_value);
+LGBCU_API int lgbcu_valid_copy_score(LgbCuContext* ctx, int32_t set, double* out, int32_t n);
+
+/* metrics: Metric::Eval of src/metric/regression_metric.hpp (l2, rmse), binary_metric.hpp (binary_logloss, auc),
+ * rank_metric.hpp + dcg_calculator.cpp (ndcg@k).  lgbcu_eval_set_ndcg uploads what NDCGMetric::Init prepares on the
+ * host: eval positions, 1/maxDCG per (query, position) (<= 0 marks an all-irrelevant query), optional query weights,
+ * the label gains and the position discounts. */
+#define LGBCU_METRIC_L2 0
+#define LGBCU_METRIC_RMSE 1
+#define LGBCU_METRIC_BINARY_LOGLOSS 2
+#define LGBCU_METRIC_AUC 3
+#define LGBCU_METRIC_NDCG 4
+LGBCU_API int lgbcu_eval_set_ndcg(LgbCuContext* ctx, int32_t set, const int32_t* eval_at, int32_t num_eval,
+                                  const double* inv_max_dcg, const float* query_weight, const double* label_gain,
+                                  int32_t num_label_gain, const double* discount, int32_t num_discount);
+/* out[0] for the point-wise metrics and auc, out[0..num_eval) for ndcg; `sigmoid` is used by binary_logloss only */
+LGBCU_API int lgbcu_eval(LgbCuContext* ctx, int32_t set, int32_t kind, double sigmoid, double* out, int32_t out_len);
+
 /* instrumentation for bench.py: device-time (ms, CUDA events on the context's stream) spent in the histogram
  * kernel since the last reset, its launch count and the algorithmic bytes it processed
  * (n*(G+8) [+4n if indexed] + total_bin*16 per call). */

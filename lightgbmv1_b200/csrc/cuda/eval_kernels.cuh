@@ -1,0 +1,156 @@
+// Validation-set scoring and evaluation metrics on the device.
+//
+// Replaces, for data sets other than the training rows: ScoreUpdater (src/boosting/score_updater.hpp:21-125) with
+// Tree::AddPredictionToScore on binned data (src/io/tree.cpp:109-199), and the metrics the path's objectives default
+// to -- L2 / RMSE (src/metric/regression_metric.hpp), binary logloss and AUC (src/metric/binary_metric.hpp:20-270),
+// NDCG@k (src/metric/rank_metric.hpp:20-160, src/metric/dcg_calculator.cpp:43-153) -- so that a run with
+// metric_freq = 1 never copies scores to the host.
+//
+// Sums are formed in double by a fixed two-stage tree (per-block partials, then one block), so a metric is bit-
+// reproducible from run to run; the reference reduces over OpenMP threads, i.e. in a thread-count-dependent order,
+// and agreement with it is to rounding (tests: 1e-9 relative; north_star asks for 1e-5).
+#pragma once
+#include <cub/device/device_radix_sort.cuh>
+#include <cub/device/device_reduce.cuh>
+#include <cub/device/device_scan.cuh>
+
+namespace {
+
+#define EVAL_THREADS 256
+#define EVAL_MAX_BLOCKS 1024
+
+__device__ __forceinline__ double block_sum_f64(double v, double* s_warp) {
+  for (int o = 16; o > 0; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);
+  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+  if (lane == 0) s_warp[warp] = v;
+  __syncthreads();
+  double t = 0.0;
+  if (threadIdx.x == 0) for (int w = 0; w < EVAL_THREADS / 32; ++w) t += s_warp[w];
+  __syncthreads();
+  return t;  // valid in thread 0
+}
+
+// kind 0: (score - label)^2 [* w]   (RegressionMetric<L2Metric>::LossOnPoint)
+// kind 1: binary logloss of prob = 1 / (1 + exp(-sigmoid * score))   (BinaryLoglossMetric::LossOnPoint, kEpsilon clip)
+__global__ void __launch_bounds__(EVAL_THREADS) k_eval_pointwise(int n, int kind, double sigmoid, const double* __restrict__ score,
+                                                                 const float* __restrict__ label, const float* __restrict__ weight,
+                                                                 double* __restrict__ partial) {
+  __shared__ double s_warp[EVAL_THREADS / 32];
+  double acc = 0.0;
+  for (int i = blockIdx.x * blockDim.x + threadIdx.x; i < n; i += gridDim.x * blockDim.x) {
+    const double s = score[i];
+    const float y = label[i];
+    double loss;
+    if (kind == 0) {
+      loss = (s - y) * (s - y);
+    } else {
+      const double prob = 1.0f / (1.0f + exp(-sigmoid * s));  // BinaryLogloss::ConvertOutput
+      if (y <= 0) loss = (1.0f - prob > LGB_EPS) ? -log(1.0f - prob) : -log(LGB_EPS);
+      else loss = (prob > LGB_EPS) ? -log(prob) : -log(LGB_EPS);
+    }
+    acc += weight ? loss * weight[i] : loss;
+  }
+  const double t = block_sum_f64(acc, s_warp);
+  if (threadIdx.x == 0) partial[blockIdx.x] = t;
+}
+
+__global__ void __launch_bounds__(EVAL_THREADS) k_sum_f32(int n, const float* __restrict__ v, double* __restrict__ partial) {
+  __shared__ double s_warp[EVAL_THREADS / 32];
+  double acc = 0.0;
+  for (int i = blockIdx.x * blockDim.x + threadIdx.x; i < n; i += gridDim.x * blockDim.x) acc += v[i];
+  const double t = block_sum_f64(acc, s_warp);
+  if (threadIdx.x == 0) partial[blockIdx.x] = t;
+}
+
+// second stage: one block sums `m` partials per output column in index order
+__global__ void __launch_bounds__(EVAL_THREADS) k_eval_final(int m, int ncol, const double* __restrict__ partial, double* __restrict__ out) {
+  __shared__ double s_warp[EVAL_THREADS / 32];
+  for (int c = 0; c < ncol; ++c) {
+    double acc = 0.0;
+    for (int i = threadIdx.x; i < m; i += blockDim.x) acc += partial[(size_t)i * ncol + c];
+    const double t = block_sum_f64(acc, s_warp);
+    if (threadIdx.x == 0) out[c] = t;
+  }
+}
+
+// ---- AUC (AUCMetric::Eval): rows sorted by score descending; per group of equal scores (pos, neg) weights; then
+//      accum = sum_g neg_g * (0.5 * pos_g + pos before g)
+__global__ void k_auc_keys(int n, const double* __restrict__ score, const float* __restrict__ label, const float* __restrict__ weight,
+                           unsigned long long* __restrict__ keys, double2* __restrict__ vals) {
+  for (int i = blockIdx.x * blockDim.x + threadIdx.x; i < n; i += gridDim.x * blockDim.x) {
+    double s = score[i];
+    if (s == 0.0) s = 0.0;  // -0.0 and +0.0 compare equal in the reference: give them one key
+    unsigned long long u = (unsigned long long)__double_as_longlong(s);
+    u = (u >> 63) ? ~u : (u | 0x8000000000000000ull);  // order-preserving
+    keys[i] = u;
+    const double w = weight ? (double)weight[i] : 1.0;
+    vals[i] = label[i] > 0 ? make_double2(w, 0.0) : make_double2(0.0, w);
+  }
+}
+struct PairSum {
+  __device__ __forceinline__ double2 operator()(const double2& a, const double2& b) const { return make_double2(a.x + b.x, a.y + b.y); }
+};
+// groups arrive in ASCENDING key order (cub's ReduceByKey keeps input order; the sort is ascending): "positives with a
+// higher score" = total positives - inclusive prefix.
+__global__ void __launch_bounds__(EVAL_THREADS) k_auc_accum(const int* __restrict__ num_groups, const double2* __restrict__ grp,
+                                                            const double* __restrict__ pos_incl, double* __restrict__ partial) {
+  __shared__ double s_warp[EVAL_THREADS / 32];
+  const int m = *num_groups;
+  const double total_pos = m > 0 ? pos_incl[m - 1] : 0.0;
+  double acc = 0.0;
+  for (int i = blockIdx.x * blockDim.x + threadIdx.x; i < m; i += gridDim.x * blockDim.x) {
+    const double2 g = grp[i];
+    acc += g.y * (g.x * 0.5f + (total_pos - pos_incl[i]));
+  }
+  const double t = block_sum_f64(acc, s_warp);
+  if (threadIdx.x == 0) { partial[2 * blockIdx.x] = t; partial[2 * blockIdx.x + 1] = blockIdx.x == 0 ? total_pos : 0.0; }
+}
+__global__ void k_auc_pos(int n, const double2* __restrict__ grp, double* __restrict__ pos) {
+  for (int i = blockIdx.x * blockDim.x + threadIdx.x; i < n; i += gridDim.x * blockDim.x) pos[i] = grp[i].x;
+}
+
+// ---- NDCG@k (NDCGMetric::Eval + DCGCalculator::CalDCG): one block per query.  rank of a document = number of
+//      documents that a stable descending sort puts before it; the top-K contributions are summed in rank order by one
+//      thread, exactly as the reference's sequential loop does.
+#define NDCG_MAX_K 1024
+__global__ void __launch_bounds__(EVAL_THREADS) k_ndcg(int num_queries, const int* __restrict__ qb, const double* __restrict__ score,
+                                                       const float* __restrict__ label, const float* __restrict__ query_weight,
+                                                       const double* __restrict__ label_gain, const double* __restrict__ discount,
+                                                       const int* __restrict__ eval_at, int num_eval, int max_k,
+                                                       const double* __restrict__ inv_max_dcg, double* __restrict__ per_query) {
+  __shared__ double s_contrib[NDCG_MAX_K];
+  for (int q = blockIdx.x; q < num_queries; q += gridDim.x) {
+    const int b = qb[q], cnt = qb[q + 1] - b;
+    double* out = per_query + (size_t)q * num_eval;
+    const double w = query_weight ? (double)query_weight[q] : 1.0;
+    if (inv_max_dcg[(size_t)q * num_eval] <= 0.0) {  // all documents irrelevant: counts as 1 (unweighted, as the reference adds it)
+      if (threadIdx.x < num_eval) out[threadIdx.x] = 1.0;
+      continue;
+    }
+    const int kk = max_k < cnt ? max_k : cnt;
+    for (int r = threadIdx.x; r < kk; r += blockDim.x) s_contrib[r] = 0.0;
+    __syncthreads();
+    for (int i = threadIdx.x; i < cnt; i += blockDim.x) {
+      const double si = score[b + i];
+      int rank = 0;
+      for (int j = 0; j < cnt; ++j) {
+        const double sj = score[b + j];
+        rank += (sj > si) || (sj == si && j < i);
+      }
+      if (rank < kk) s_contrib[rank] = label_gain[(int)label[b + i]] * discount[rank];
+    }
+    __syncthreads();
+    if (threadIdx.x == 0) {
+      double cur = 0.0; int left = 0;
+      for (int e = 0; e < num_eval; ++e) {
+        int k = eval_at[e]; if (k > cnt) k = cnt;
+        for (int j = left; j < k; ++j) cur += s_contrib[j];
+        out[e] = cur * inv_max_dcg[(size_t)q * num_eval + e] * w;
+        left = k;
+      }
+    }
+    __syncthreads();
+  }
+}
+
+}  // namespace

@@ -2,6 +2,7 @@
 // See include/lgbcu.h for the contract of each entry point and the reference code it stands in for.
 #include <algorithm>
 #include <atomic>
+#include <cmath>
 #include <cstddef>
 #include <cstdarg>
 #include <cstdio>
@@ -65,8 +66,33 @@ struct RankParams {
   double sigmoid = 1.0; int truncation_level = 20; int norm = 1;
 };
 
+// NDCG tables of one score set (NDCGMetric::Init prepares them on the host)
+struct NdcgTables {
+  int* d_eval_at = nullptr; int num_eval = 0, max_k = 0;
+  double* d_inv_max_dcg = nullptr; float* d_query_weight = nullptr; double sum_query_weights = 0.0;
+  double* d_label_gain = nullptr; double* d_discount = nullptr;
+  bool ready = false;
+};
+
+// A validation set: bins from the training mappers + its own score vector and meta data
+struct ValidSet {
+  int n = 0;
+  uint8_t* d_bins = nullptr;   // row-major, same stride as the training matrix
+  double* d_score = nullptr;
+  float* d_label = nullptr; float* d_weight = nullptr;
+  int* d_query = nullptr; int num_queries = 0;
+  NdcgTables ndcg;
+};
+
 struct LgbCuContext {
   int device = 0;
+  std::vector<ValidSet> valid;
+  NdcgTables train_ndcg;
+  // evaluation scratch (grown on demand)
+  double* d_eval_partial = nullptr; double* d_eval_out = nullptr; double* h_eval_out = nullptr;
+  unsigned long long* d_auc_keys[2] = {nullptr, nullptr}; double2* d_auc_vals[2] = {nullptr, nullptr};
+  double* d_auc_pos = nullptr; int* d_auc_groups = nullptr; void* d_cub_tmp = nullptr; size_t cub_tmp_bytes = 0; int auc_cap = 0;
+  double* d_ndcg_per_query = nullptr; size_t ndcg_cap = 0;
   // data-parallel
   ncclComm_t comm = nullptr; int rank = 0, world = 1;
   int num_sms = 148;
@@ -226,12 +252,39 @@ int comm_reduce_hist(LgbCuContext* c, int split_index) {
   return 0;
 }
 
+// host tree arrays -> device (shared by the training-set and validation-set tree walks)
+int upload_tree(LgbCuContext* c, int32_t num_leaves, const int32_t* split_feature_inner, const int32_t* threshold_bin,
+                const int8_t* decision_type, const int32_t* left_child, const int32_t* right_child,
+                const double* leaf_value, TreeDev* T) {
+  NEED(split_feature_inner && threshold_bin && decision_type && left_child && right_child, "add_score_by_tree: NULL tree array");
+  const int ni = num_leaves - 1;
+  if (c->tree_cap < num_leaves) {
+    CU(dev_alloc(&c->d_tree_i32, (size_t)4 * num_leaves));
+    CU(dev_alloc(&c->d_tree_i8, (size_t)num_leaves));
+    CU(dev_alloc(&c->d_tree_f64, (size_t)num_leaves));
+    c->tree_cap = num_leaves;
+  }
+  for (int i = 0; i < ni; ++i) NEED(split_feature_inner[i] >= 0 && split_feature_inner[i] < c->F, "add_score_by_tree: split feature out of range");
+  int* d_feat = c->d_tree_i32, *d_thr = d_feat + num_leaves, *d_lc = d_thr + num_leaves, *d_rc = d_lc + num_leaves;
+  CU(cudaMemcpyAsync(d_feat, split_feature_inner, sizeof(int) * ni, cudaMemcpyHostToDevice, c->stream));
+  CU(cudaMemcpyAsync(d_thr, threshold_bin, sizeof(int) * ni, cudaMemcpyHostToDevice, c->stream));
+  CU(cudaMemcpyAsync(d_lc, left_child, sizeof(int) * ni, cudaMemcpyHostToDevice, c->stream));
+  CU(cudaMemcpyAsync(d_rc, right_child, sizeof(int) * ni, cudaMemcpyHostToDevice, c->stream));
+  CU(cudaMemcpyAsync(c->d_tree_i8, decision_type, ni, cudaMemcpyHostToDevice, c->stream));
+  CU(cudaMemcpyAsync(c->d_tree_f64, leaf_value, sizeof(double) * num_leaves, cudaMemcpyHostToDevice, c->stream));
+  T->split_feature = d_feat; T->threshold_bin = d_thr; T->decision_type = c->d_tree_i8; T->left_child = d_lc; T->right_child = d_rc;
+  T->leaf_value = c->d_tree_f64; T->num_leaves = num_leaves;
+  return 0;
+}
+
+void free_valid_sets(LgbCuContext* c);
 int rank_prepare(LgbCuContext* c);
 int rank_launch(LgbCuContext* c);
 
 }  // namespace
 
 #include "rank_kernels.cuh"
+#include "eval_kernels.cuh"
 
 extern "C" {
 
@@ -328,6 +381,7 @@ int lgbcu_destroy(LgbCuContext* c) {
   cudaStreamSynchronize(c->stream);
   drop_graph(c);
   lgbcu_comm_destroy(c);
+  free_valid_sets(c);
   void* ptrs[] = {c->d_bins, c->d_feats, c->d_feat_used, c->d_grad, c->d_hess, c->d_gh, c->d_label, c->d_weight, c->d_score,
                   c->d_indices[0], c->d_indices[1], c->d_part_bits, c->d_part_sync, c->d_bins_col, c->d_query, c->d_label_gain,
                   c->d_inv_max_dcg, c->d_sigmoid_table, c->d_pool, c->d_splittable, c->d_leaves, c->d_best,
@@ -659,22 +713,8 @@ int lgbcu_add_score_by_tree(LgbCuContext* c, int32_t num_leaves, const int32_t* 
     NEED(rows == nullptr, "lgbcu_add_score_by_tree: constant tree over a row subset is not supported");
     return lgbcu_add_score_const(c, leaf_value[0]);
   }
-  NEED(split_feature_inner && threshold_bin && decision_type && left_child && right_child, "lgbcu_add_score_by_tree: NULL tree array");
-  const int ni = num_leaves - 1;
-  if (c->tree_cap < num_leaves) {
-    CU(dev_alloc(&c->d_tree_i32, (size_t)4 * num_leaves));
-    CU(dev_alloc(&c->d_tree_i8, (size_t)num_leaves));
-    CU(dev_alloc(&c->d_tree_f64, (size_t)num_leaves));
-    c->tree_cap = num_leaves;
-  }
-  for (int i = 0; i < ni; ++i) NEED(split_feature_inner[i] >= 0 && split_feature_inner[i] < c->F, "lgbcu_add_score_by_tree: split feature out of range");
-  int* d_feat = c->d_tree_i32, *d_thr = d_feat + num_leaves, *d_lc = d_thr + num_leaves, *d_rc = d_lc + num_leaves;
-  CU(cudaMemcpyAsync(d_feat, split_feature_inner, sizeof(int) * ni, cudaMemcpyHostToDevice, c->stream));
-  CU(cudaMemcpyAsync(d_thr, threshold_bin, sizeof(int) * ni, cudaMemcpyHostToDevice, c->stream));
-  CU(cudaMemcpyAsync(d_lc, left_child, sizeof(int) * ni, cudaMemcpyHostToDevice, c->stream));
-  CU(cudaMemcpyAsync(d_rc, right_child, sizeof(int) * ni, cudaMemcpyHostToDevice, c->stream));
-  CU(cudaMemcpyAsync(c->d_tree_i8, decision_type, ni, cudaMemcpyHostToDevice, c->stream));
-  CU(cudaMemcpyAsync(c->d_tree_f64, leaf_value, sizeof(double) * num_leaves, cudaMemcpyHostToDevice, c->stream));
+  TreeDev T;
+  if (upload_tree(c, num_leaves, split_feature_inner, threshold_bin, decision_type, left_child, right_child, leaf_value, &T)) return -1;
   const int* d_rows = nullptr;
   if (rows) {
     const bool reuse = rows_tag != 0 && rows_tag == c->rows_tag && num_rows == c->rows_count;
@@ -685,9 +725,6 @@ int lgbcu_add_score_by_tree(LgbCuContext* c, int32_t num_leaves, const int32_t* 
     }
     d_rows = c->d_rows;
   }
-  TreeDev T;
-  T.split_feature = d_feat; T.threshold_bin = d_thr; T.decision_type = c->d_tree_i8; T.left_child = d_lc; T.right_child = d_rc;
-  T.leaf_value = c->d_tree_f64; T.num_leaves = num_leaves;
   LAUNCH(k_add_score_tree, grid_for(c, n, 256), 256, 0, c->stream, c->view(), T, d_rows, n, c->d_score);
   CU(cudaGetLastError());
   CU(cudaStreamSynchronize(c->stream));  // the caller's host arrays may go away
@@ -1047,5 +1084,7 @@ int lgbcu_comm_destroy(LgbCuContext* c) {
 }
 
 }  // extern "C"
+
+#include "valid_eval.cuh"
 
 #include "noalloc_partition.cuh"
