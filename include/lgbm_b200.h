@@ -13,6 +13,7 @@
 #ifndef LGBM_B200_H_
 #define LGBM_B200_H_
 
+#include <stddef.h>
 #include <stdint.h>
 
 #ifdef __cplusplus
@@ -63,9 +64,18 @@ LGBM_B200_API int LGBM_BoosterNumModelPerIteration(BoosterHandle handle, int* ou
 LGBM_B200_API int LGBM_BoosterNumberOfTotalModel(BoosterHandle handle, int* out_models);
 /* c_api.h:496-497 */
 LGBM_B200_API int LGBM_BoosterGetNumClasses(BoosterHandle handle, int* out_len);
-/* c_api.h:649-651  data_idx 0 = training data */
+/* c_api.h:469-470  the data set must have been created with `reference` = the training data (same bin mappers);
+ * its scores live on the device and every new tree is added to them */
+LGBM_B200_API int LGBM_BoosterAddValidData(BoosterHandle handle, const DatasetHandle valid_data);
+/* c_api.h:575-576, 590-595, 636-639  metrics: l2, rmse, binary_logloss, auc, ndcg@k (evaluated on the device);
+ * data_idx 0 = training data, i = i-th validation set */
+LGBM_B200_API int LGBM_BoosterGetEvalCounts(BoosterHandle handle, int* out_len);
+LGBM_B200_API int LGBM_BoosterGetEvalNames(BoosterHandle handle, const int len, int* out_len, const size_t buffer_len,
+                                           size_t* out_buffer_len, char** out_strs);
+LGBM_B200_API int LGBM_BoosterGetEval(BoosterHandle handle, int data_idx, int* out_len, double* out_results);
+/* c_api.h:649-651  data_idx 0 = training data, i = i-th validation set */
 LGBM_B200_API int LGBM_BoosterGetNumPredict(BoosterHandle handle, int data_idx, int64_t* out_len);
-/* c_api.h:663-666  scores of the training data after the objective's output transform */
+/* c_api.h:663-666  scores of the training / validation data after the objective's output transform */
 LGBM_B200_API int LGBM_BoosterGetPredict(BoosterHandle handle, int data_idx, int64_t* out_len, double* out_result);
 /* c_api.h:1007-1018  predict_type: C_API_PREDICT_NORMAL | C_API_PREDICT_RAW_SCORE (host tree walk; not on the hot path) */
 LGBM_B200_API int LGBM_BoosterPredictForMat(BoosterHandle handle, const void* data, int data_type, int32_t nrow, int32_t ncol,

@@ -44,7 +44,8 @@ __global__ void __launch_bounds__(EVAL_THREADS) k_eval_pointwise(int n, int kind
     if (kind == 0) {
       loss = (s - y) * (s - y);
     } else {
-      const double prob = 1.0f / (1.0f + exp(-sigmoid * s));  // BinaryLogloss::ConvertOutput
+      // BinaryLogloss::ConvertOutput; sigmoid <= 0 = no objective (custom): the score is taken as the probability
+      const double prob = sigmoid > 0.0 ? 1.0f / (1.0f + exp(-sigmoid * s)) : s;
       if (y <= 0) loss = (1.0f - prob > LGB_EPS) ? -log(1.0f - prob) : -log(LGB_EPS);
       else loss = (prob > LGB_EPS) ? -log(prob) : -log(LGB_EPS);
     }

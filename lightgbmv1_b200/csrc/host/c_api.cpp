@@ -151,18 +151,67 @@ int LGBM_BoosterGetNumClasses(BoosterHandle handle, int* out_len) {
 
 int LGBM_BoosterGetNumPredict(BoosterHandle handle, int data_idx, int64_t* out_len) {
   API_BEGIN();
-  if (data_idx != 0) Log::Fatal("only the training data (data_idx = 0) is attached to this booster");
-  *out_len = reinterpret_cast<Booster*>(handle)->gbdt->num_data();
+  GBDT* g = reinterpret_cast<Booster*>(handle)->gbdt.get();
+  if (data_idx < 0 || data_idx > g->num_valid()) Log::Fatal("Check failed: data_idx >= 0 && data_idx <= number of validation sets");
+  *out_len = data_idx == 0 ? g->num_data() : g->valid_num_data(data_idx - 1);
   API_END();
 }
 
 int LGBM_BoosterGetPredict(BoosterHandle handle, int data_idx, int64_t* out_len, double* out_result) {
   API_BEGIN();
-  if (data_idx != 0) Log::Fatal("only the training data (data_idx = 0) is attached to this booster");
   Booster* b = reinterpret_cast<Booster*>(handle);
   std::lock_guard<std::mutex> lock(b->mu);
-  b->gbdt->GetTrainScore(out_result, true);
-  *out_len = b->gbdt->num_data();
+  if (data_idx < 0 || data_idx > b->gbdt->num_valid()) Log::Fatal("Check failed: data_idx >= 0 && data_idx <= number of validation sets");
+  if (data_idx == 0) {
+    b->gbdt->GetTrainScore(out_result, true);
+    *out_len = b->gbdt->num_data();
+  } else {
+    b->gbdt->GetValidScore(data_idx - 1, out_result, true);
+    *out_len = b->gbdt->valid_num_data(data_idx - 1);
+  }
+  API_END();
+}
+
+int LGBM_BoosterAddValidData(BoosterHandle handle, const DatasetHandle valid_data) {
+  API_BEGIN();
+  if (!valid_data) Log::Fatal("validation data handle is NULL");
+  Booster* b = reinterpret_cast<Booster*>(handle);
+  std::lock_guard<std::mutex> lock(b->mu);
+  b->gbdt->AddValidData(reinterpret_cast<const Dataset*>(valid_data));
+  API_END();
+}
+
+int LGBM_BoosterGetEvalCounts(BoosterHandle handle, int* out_len) {
+  API_BEGIN();
+  *out_len = static_cast<int>(reinterpret_cast<Booster*>(handle)->gbdt->EvalNames().size());
+  API_END();
+}
+
+int LGBM_BoosterGetEvalNames(BoosterHandle handle, const int len, int* out_len, const size_t buffer_len,
+                             size_t* out_buffer_len, char** out_strs) {
+  API_BEGIN();
+  const std::vector<std::string> names = reinterpret_cast<Booster*>(handle)->gbdt->EvalNames();
+  *out_buffer_len = 0;
+  int idx = 0;
+  for (const std::string& name : names) {  // Booster::GetEvalNames (src/c_api.cpp:764-780)
+    if (idx < len && buffer_len > 0) {
+      std::memcpy(out_strs[idx], name.c_str(), std::min(name.size() + 1, buffer_len));
+      out_strs[idx][buffer_len - 1] = '\0';
+    }
+    *out_buffer_len = std::max(name.size() + 1, *out_buffer_len);
+    ++idx;
+  }
+  *out_len = idx;
+  API_END();
+}
+
+int LGBM_BoosterGetEval(BoosterHandle handle, int data_idx, int* out_len, double* out_results) {
+  API_BEGIN();
+  Booster* b = reinterpret_cast<Booster*>(handle);
+  std::lock_guard<std::mutex> lock(b->mu);
+  const std::vector<double> r = b->gbdt->GetEvalAt(data_idx);
+  *out_len = static_cast<int>(r.size());
+  for (size_t i = 0; i < r.size(); ++i) out_results[i] = r[i];
   API_END();
 }
 

@@ -38,7 +38,8 @@ const std::unordered_map<std::string, std::string>& Aliases() {
       {"subsample_for_bin", "bin_construct_sample_cnt"}, {"data_seed", "data_random_seed"},
       {"is_enable_bundle", "enable_bundle"}, {"bundle", "enable_bundle"},
       {"unbalance", "is_unbalance"}, {"unbalanced_sets", "is_unbalance"},
-      {"metrics", "metric"}, {"metric_types", "metric"}, {"num_machine", "num_machines"},
+      {"metrics", "metric"}, {"metric_types", "metric"}, {"ndcg_eval_at", "eval_at"}, {"ndcg_at", "eval_at"},
+      {"map_eval_at", "eval_at"}, {"map_at", "eval_at"}, {"num_machine", "num_machines"},
       {"feature_contrib", "feature_contri"}, {"fc", "feature_contri"}, {"fp", "feature_contri"}, {"feature_penalty", "feature_contri"},
       {"num_classes", "num_class"},
   };
@@ -78,6 +79,24 @@ bool GetBool(const std::unordered_map<std::string, std::string>& m, const char* 
   else Log::Fatal("Parameter %s should be \"true\"/\"+\" or \"false\"/\"-\", got \"%s\"", k, s.c_str());
   return true;
 }
+// ParseMetricAlias (include/LightGBM/config.h:1116-1146)
+std::string MetricAlias(const std::string& t) {
+  auto in = [&](std::initializer_list<const char*> l) { for (auto* x : l) if (t == x) return true; return false; };
+  if (in({"regression", "regression_l2", "l2", "mean_squared_error", "mse"})) return "l2";
+  if (in({"l2_root", "root_mean_squared_error", "rmse"})) return "rmse";
+  if (in({"regression_l1", "l1", "mean_absolute_error", "mae"})) return "l1";
+  if (in({"binary_logloss", "binary"})) return "binary_logloss";
+  if (in({"ndcg", "lambdarank", "rank_xendcg", "xendcg", "xe_ndcg", "xe_ndcg_mart", "xendcg_mart"})) return "ndcg";
+  if (in({"map", "mean_average_precision"})) return "map";
+  if (in({"multi_logloss", "multiclass", "softmax", "multiclassova", "multiclass_ova", "ova", "ovr"})) return "multi_logloss";
+  if (in({"xentropy", "cross_entropy"})) return "cross_entropy";
+  if (in({"xentlambda", "cross_entropy_lambda"})) return "cross_entropy_lambda";
+  if (in({"kldiv", "kullback_leibler"})) return "kullback_leibler";
+  if (in({"mean_absolute_percentage_error", "mape"})) return "mape";
+  if (in({"none", "null", "custom", "na"})) return "custom";
+  return t;
+}
+
 std::vector<double> ParseDoubles(const std::string& s) {
   std::vector<double> v;
   for (auto& t : SplitAny(s, ",")) v.push_back(std::strtod(t.c_str(), nullptr));
@@ -142,7 +161,30 @@ void Config::Set(const std::unordered_map<std::string, std::string>& p) {
     else Log::Fatal("boosting=%s is outside this library's path (only gbdt is built)", s.c_str());
   }
   if (GetStr(p, "objective", &s)) objective = ObjectiveAlias(s);
-  if (GetStr(p, "metric", &s)) metric = SplitAny(s, ",");
+  // GetMetricType (src/io/config.cpp:87-100): lower-case, split on ',', ParseMetricAlias, drop repeats; with no
+  // `metric` given at all the objective names the metric.
+  {
+    std::string mv;
+    const bool given = GetStr(p, "metric", &mv);
+    std::transform(mv.begin(), mv.end(), mv.begin(), ::tolower);
+    metric.clear();
+    auto add = [&](const std::string& raw_name) {
+      const std::string t = MetricAlias(raw_name);
+      if (std::find(metric.begin(), metric.end(), t) == metric.end()) metric.push_back(t);
+    };
+    if (given) for (auto& m : SplitAny(mv, ",")) add(m);
+    if (metric.empty() && mv.empty()) {
+      std::string ov;
+      if (GetStr(p, "objective", &ov)) {
+        std::transform(ov.begin(), ov.end(), ov.begin(), ::tolower);
+        for (auto& m : SplitAny(ov, ",")) add(m);
+      }
+    }
+  }
+  if (GetStr(p, "eval_at", &s)) {
+    eval_at.clear();
+    for (double d : ParseDoubles(s)) eval_at.push_back(static_cast<int>(d));
+  }
   if (GetStr(p, "device_type", &s)) {
     std::transform(s.begin(), s.end(), s.begin(), ::tolower);
     // the reference accepts cpu|gpu (src/io/config.cpp:121-133); here every value selects the CUDA learner,

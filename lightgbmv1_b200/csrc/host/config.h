@@ -14,7 +14,8 @@ struct Config {
   std::string boosting = "gbdt";
   std::string tree_learner = "serial";
   std::string device_type = "cuda";
-  std::vector<std::string> metric;
+  std::vector<std::string> metric;   // normalised names (ParseMetricAlias), in the order given
+  std::vector<int> eval_at;          // NDCG positions; empty = 1..5 (DCGCalculator::DefaultEvalAt)
   int num_iterations = 100;
   double learning_rate = 0.1;
   int num_leaves = 31;

@@ -6,6 +6,7 @@
 #include <omp.h>
 
 #include <algorithm>
+#include <cmath>
 #include <cstring>
 
 namespace lgb {
@@ -84,6 +85,24 @@ GBDT::GBDT(const Dataset* train, const Config& config)
   }
   records_.resize(std::max(config_.num_leaves - 1, 1));
   st.tick("labels/objective/comm");
+  // ---- metrics (Metric::CreateMetric, src/metric/metric.cpp:16-63; "custom" yields none)
+  eval_at_ = config_.eval_at;
+  if (eval_at_.empty()) { for (int i = 1; i <= 5; ++i) eval_at_.push_back(i); }  // DCGCalculator::DefaultEvalAt
+  for (int k : eval_at_) if (k <= 0) Log::Fatal("Check failed: eval_at > 0");
+  for (const std::string& m : config_.metric) {
+    MetricSpec spec;
+    if (m == "l2") { spec.kind = LGBCU_METRIC_L2; spec.names = {"l2"}; }
+    else if (m == "rmse") { spec.kind = LGBCU_METRIC_RMSE; spec.names = {"rmse"}; }
+    else if (m == "binary_logloss") { spec.kind = LGBCU_METRIC_BINARY_LOGLOSS; spec.names = {"binary_logloss"}; }
+    else if (m == "auc") { spec.kind = LGBCU_METRIC_AUC; spec.names = {"auc"}; }
+    else if (m == "ndcg") {
+      spec.kind = LGBCU_METRIC_NDCG;
+      for (int k : eval_at_) spec.names.push_back("ndcg@" + std::to_string(k));
+    }
+    else if (m == "custom") continue;
+    else Log::Fatal("metric=%s is outside this library's path (l2, rmse, binary_logloss, auc, ndcg)", m.c_str());
+    metrics_.push_back(spec);
+  }
 
   // ---- ResetBaggingConfig (gbdt.cpp:739-797)
   if (config_.bagging_fraction < 1.0 && config_.bagging_freq > 0) {
@@ -158,6 +177,7 @@ bool GBDT::TrainOneIter(const float* grad, const float* hess) {
       if (std::fabs(s) > kEpsilon) {
         init_score = s;
         Check(lgbcu_add_score_const(ctx_, init_score));
+        for (const ValidEntry& v : valid_) Check(lgbcu_valid_add_const(ctx_, v.set, init_score));
         Log::Info("Start training from score %lf", init_score);
       }
     }
@@ -199,6 +219,7 @@ bool GBDT::TrainOneIter(const float* grad, const float* hess) {
                                     tree->decision_type().data(), tree->left_child().data(), tree->right_child().data(),
                                     tree->leaf_values().data(), bag_indices_.data() + bag_cnt_, N - bag_cnt_, bag_version_));
     }
+    AddTreeToValid(*tree);
     if (std::fabs(init_score) > kEpsilon) tree->AddBias(init_score);
   } else {
     if (models_.empty()) {  // only add default score one-time (gbdt.cpp:385-401)
@@ -207,6 +228,7 @@ bool GBDT::TrainOneIter(const float* grad, const float* hess) {
       else output = init_score;
       tree->AsConstantTree(output);
       Check(lgbcu_add_score_const(ctx_, output));
+      for (const ValidEntry& v : valid_) Check(lgbcu_valid_add_const(ctx_, v.set, output));
     }
   }
   st.tick("tree + score update");
@@ -223,6 +245,141 @@ bool GBDT::TrainOneIter(const float* grad, const float* hess) {
 void GBDT::GetTrainScore(double* out, bool converted) const {
   const int N = train_->num_data();
   Check(lgbcu_copy_score(ctx_, out, N));
+  if (converted && objective_) {
+#pragma omp parallel for schedule(static)
+    for (int i = 0; i < N; ++i) { double v = out[i]; objective_->ConvertOutput(&v, &out[i]); }
+  }
+}
+
+// ---- validation data and metrics ----------------------------------------------------------------------------------
+
+void GBDT::AddTreeToValid(const Tree& tree) {
+  if (valid_.empty()) return;
+  std::vector<int> thr(tree.threshold_in_bin().begin(), tree.threshold_in_bin().end());
+  for (const ValidEntry& v : valid_) {
+    Check(lgbcu_valid_add_tree(ctx_, v.set, tree.num_leaves(), tree.split_feature_inner().data(), thr.data(),
+                               tree.decision_type().data(), tree.left_child().data(), tree.right_child().data(),
+                               tree.leaf_values().data()));
+  }
+}
+
+// GBDT::AddValidDataset (gbdt.cpp:121-149)
+void GBDT::AddValidData(const Dataset* valid) {
+  // Dataset::CheckAlign: same features, same bin mappers
+  bool aligned = valid->num_features() == train_->num_features() && valid->num_total_features() == train_->num_total_features();
+  if (aligned) aligned = valid->feature_infos() == train_->feature_infos();
+  for (int f = 0; aligned && f < train_->num_features(); ++f) aligned = valid->real_feature_index(f) == train_->real_feature_index(f);
+  if (!aligned) Log::Fatal("Cannot add validation data, since it has different bin mappers with training data");
+  ValidEntry e;
+  e.data = valid;
+  Check(lgbcu_valid_create(ctx_, valid->num_data(), valid->bins().data(), &e.set));
+  const Metadata& md = valid->metadata();
+  const int n = valid->num_data();
+  if (!md.label.empty()) Check(lgbcu_valid_set_label(ctx_, e.set, md.label.data(), n));
+  if (!md.weights.empty()) Check(lgbcu_valid_set_weight(ctx_, e.set, md.weights.data(), n));
+  if (!md.query_boundaries.empty())
+    Check(lgbcu_valid_set_query(ctx_, e.set, md.query_boundaries.data(), static_cast<int>(md.query_boundaries.size()) - 1));
+  if (!md.init_score.empty()) Check(lgbcu_valid_set_score(ctx_, e.set, md.init_score.data(), n));  // ScoreUpdater ctor
+  valid_.push_back(e);
+  // the trees grown so far
+  for (const auto& t : models_) {
+    std::vector<int> thr(t->threshold_in_bin().begin(), t->threshold_in_bin().end());
+    Check(lgbcu_valid_add_tree(ctx_, e.set, t->num_leaves(), t->split_feature_inner().data(), thr.data(),
+                               t->decision_type().data(), t->left_child().data(), t->right_child().data(),
+                               t->leaf_values().data()));
+  }
+  for (const MetricSpec& m : metrics_) {
+    if (m.kind == LGBCU_METRIC_NDCG) SetupNdcg(e.set, md, n);
+    if (md.label.empty()) Log::Fatal("Label should not be NULL");
+  }
+}
+
+// NDCGMetric::Init (rank_metric.hpp:33-75) + DCGCalculator::{Init,CheckLabel,CalMaxDCG} (dcg_calculator.cpp:43-107)
+void GBDT::SetupNdcg(int set, const Metadata& md, int num_data) {
+  if (md.query_boundaries.empty()) Log::Fatal("The NDCG metric requires query information");
+  std::vector<double> gain = config_.label_gain;
+  if (gain.empty()) {  // DefaultLabelGain: 2^i - 1
+    gain.push_back(0.0);
+    for (int i = 1; i < 31; ++i) gain.push_back(static_cast<double>((1 << i) - 1));
+  }
+  const int kMaxPosition = 10000;
+  int max_k = 0;
+  for (int k : eval_at_) max_k = std::max(max_k, k);
+  std::vector<double> discount(std::min(std::max(max_k, 1), kMaxPosition));
+  for (size_t i = 0; i < discount.size(); ++i) discount[i] = 1.0 / std::log2(2.0 + i);
+  for (int i = 0; i < num_data; ++i) {  // CheckLabel
+    const label_t l = md.label[i];
+    if (std::fabs(l - static_cast<int>(l)) > kEpsilon)
+      Log::Fatal("label should be int type (met %f) for ranking task,\nfor the gain of label, please set the label_gain parameter", l);
+    if (l < 0) Log::Fatal("Label should be non-negative (met %f) for ranking task", l);
+    if (static_cast<size_t>(l) >= gain.size())
+      Log::Fatal("Label %zu is not less than the number of label mappings (%zu)", static_cast<size_t>(l), gain.size());
+  }
+  const int nq = static_cast<int>(md.query_boundaries.size()) - 1;
+  const int ne = static_cast<int>(eval_at_.size());
+  std::vector<double> inv(static_cast<size_t>(nq) * ne, 0.0);
+#pragma omp parallel for schedule(static)
+  for (int q = 0; q < nq; ++q) {
+    const label_t* lab = md.label.data() + md.query_boundaries[q];
+    const int cnt = md.query_boundaries[q + 1] - md.query_boundaries[q];
+    std::vector<int> label_cnt(gain.size(), 0);
+    for (int i = 0; i < cnt; ++i) ++label_cnt[static_cast<int>(lab[i])];
+    double cur = 0.0;
+    int left = 0, top = static_cast<int>(gain.size()) - 1;
+    for (int e = 0; e < ne; ++e) {
+      int k = eval_at_[e];
+      if (k > cnt) k = cnt;
+      for (int j = left; j < k; ++j) {
+        while (top > 0 && label_cnt[top] <= 0) top -= 1;
+        if (top < 0) break;
+        cur += discount[j] * gain[top];
+        label_cnt[top] -= 1;
+      }
+      inv[static_cast<size_t>(q) * ne + e] = cur > 0.0 ? 1.0f / cur : -1.0f;
+      left = k;
+    }
+  }
+  std::vector<float> qw;
+  if (!md.weights.empty()) {  // Metadata::LoadQueryWeights (metadata.cpp:455-469): float mean of the row weights
+    qw.resize(nq);
+    for (int q = 0; q < nq; ++q) {
+      float w = 0.0f;
+      for (int j = md.query_boundaries[q]; j < md.query_boundaries[q + 1]; ++j) w += md.weights[j];
+      qw[q] = w / (md.query_boundaries[q + 1] - md.query_boundaries[q]);
+    }
+  }
+  Check(lgbcu_eval_set_ndcg(ctx_, set, eval_at_.data(), ne, inv.data(), qw.empty() ? nullptr : qw.data(), gain.data(),
+                            static_cast<int>(gain.size()), discount.data(), static_cast<int>(discount.size())));
+}
+
+std::vector<std::string> GBDT::EvalNames() const {
+  std::vector<std::string> out;
+  for (const MetricSpec& m : metrics_) for (const std::string& n : m.names) out.push_back(n);
+  return out;
+}
+
+// GBDT::GetEvalAt (gbdt.cpp:545-565)
+std::vector<double> GBDT::GetEvalAt(int data_idx) {
+  if (data_idx < 0 || data_idx > static_cast<int>(valid_.size())) Log::Fatal("Check failed: data_idx >= 0 && data_idx <= valid size");
+  const int set = data_idx == 0 ? -1 : valid_[data_idx - 1].set;
+  std::vector<double> ret;
+  for (const MetricSpec& m : metrics_) {
+    if (m.kind == LGBCU_METRIC_NDCG && data_idx == 0 && !train_ndcg_ready_) {
+      SetupNdcg(-1, train_->metadata(), train_->num_data());
+      train_ndcg_ready_ = true;
+    }
+    double buf[64];
+    // metrics convert the raw score through the objective (ObjectiveFunction::ConvertOutput): a sigmoid for binary
+    const double sig = (objective_ && std::string(objective_->Name()) == "binary") ? config_.sigmoid : 0.0;
+    Check(lgbcu_eval(ctx_, set, m.kind, sig, buf, 64));
+    for (size_t i = 0; i < m.names.size(); ++i) ret.push_back(buf[i]);
+  }
+  return ret;
+}
+
+void GBDT::GetValidScore(int idx, double* out, bool converted) const {
+  const int N = valid_[idx].data->num_data();
+  Check(lgbcu_valid_copy_score(ctx_, valid_[idx].set, out, N));
   if (converted && objective_) {
 #pragma omp parallel for schedule(static)
     for (int i = 0; i < N; ++i) { double v = out[i]; objective_->ConvertOutput(&v, &out[i]); }

@@ -32,6 +32,14 @@ class GBDT {
   int current_iteration() const { return static_cast<int>(models_.size()); }
   int num_data() const { return train_->num_data(); }
   void GetTrainScore(double* out, bool converted) const;      // LGBM_BoosterGetPredict(data_idx = 0)
+  // validation data and metrics (GBDT::AddValidDataset / GetEvalAt, src/boosting/gbdt.cpp:121-149, 545-565; the metric
+  // objects of src/c_api.cpp:160-172, 332-344 are the MetricSpec list here, evaluated on the device)
+  void AddValidData(const Dataset* valid);
+  int num_valid() const { return static_cast<int>(valid_.size()); }
+  int valid_num_data(int idx) const { return valid_[idx].data->num_data(); }
+  void GetValidScore(int idx, double* out, bool converted) const;  // LGBM_BoosterGetPredict(data_idx = idx + 1)
+  std::vector<double> GetEvalAt(int data_idx);
+  std::vector<std::string> EvalNames() const;
   void PredictMat(const void* data, int data_type, int32_t nrow, int32_t ncol, bool row_major, bool raw_score,
                   int num_iteration, double* out) const;
   std::string SaveModelToString(int start_iteration, int num_iteration) const;
@@ -40,6 +48,14 @@ class GBDT {
   int64_t total_device_launches() const;
 
  private:
+  struct MetricSpec { int kind; std::vector<std::string> names; };
+  struct ValidEntry { const Dataset* data; int set; };
+  void SetupNdcg(int set, const Metadata& md, int num_data);
+  void AddTreeToValid(const Tree& tree);
+  std::vector<MetricSpec> metrics_;
+  std::vector<int> eval_at_;
+  std::vector<ValidEntry> valid_;
+  bool train_ndcg_ready_ = false;
   void Bagging(int iter);
   void ResetFeatureMask();
   std::vector<double> FeatureImportanceSplit(int num_iteration) const;

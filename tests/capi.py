@@ -66,12 +66,32 @@ class LGBMLib:
                                                             h.ctypes.data_as(C.POINTER(C.c_float)), C.byref(fin)))
         return fin.value
 
-    def get_predict(self, b, n):
+    def get_predict(self, b, n, data_idx=0):
         out = np.empty(n, dtype=np.float64)
         ln = C.c_int64(0)
-        self.check(self.lib.LGBM_BoosterGetPredict(b, C.c_int(0), C.byref(ln), out.ctypes.data_as(C.POINTER(C.c_double))))
+        self.check(self.lib.LGBM_BoosterGetPredict(b, C.c_int(data_idx), C.byref(ln), out.ctypes.data_as(C.POINTER(C.c_double))))
         assert ln.value == n
         return out
+
+    def add_valid(self, b, ds):
+        self.check(self.lib.LGBM_BoosterAddValidData(b, ds))
+
+    def eval_names(self, b):
+        n = C.c_int(0)
+        self.check(self.lib.LGBM_BoosterGetEvalCounts(b, C.byref(n)))
+        bufs = [C.create_string_buffer(255) for _ in range(n.value)]
+        ptrs = (C.c_char_p * n.value)(*map(C.addressof, bufs))
+        got, need = C.c_int(0), C.c_size_t(0)
+        self.check(self.lib.LGBM_BoosterGetEvalNames(b, C.c_int(n.value), C.byref(got), C.c_size_t(255), C.byref(need), ptrs))
+        return [bufs[i].value.decode() for i in range(got.value)]
+
+    def get_eval(self, b, data_idx):
+        n = C.c_int(0)
+        self.check(self.lib.LGBM_BoosterGetEvalCounts(b, C.byref(n)))
+        out = np.zeros(max(n.value, 1), dtype=np.float64)
+        ln = C.c_int(0)
+        self.check(self.lib.LGBM_BoosterGetEval(b, C.c_int(data_idx), C.byref(ln), out.ctypes.data_as(C.POINTER(C.c_double))))
+        return out[:ln.value]
 
     def predict_mat(self, b, X, raw=False, num_iteration=-1):
         X = np.ascontiguousarray(X)
