@@ -1007,7 +1007,7 @@ extern "C" int lgbcu_debug_hist_stages(unsigned long long* out8, int reset) {
   return 0;
 }
 extern "C" int lgbcu_debug_stages(unsigned long long* out16, int reset) {
-  unsigned long long z[16] = {0};
+  unsigned long long z[32] = {0};
   cudaDeviceSynchronize();
   cudaMemcpyFromSymbol(out16, g_stage_cycles, sizeof(z));
   if (reset) cudaMemcpyToSymbol(g_stage_cycles, z, sizeof(z));

@@ -16,7 +16,7 @@
 
 #define FULL_MASK 0xffffffffu
 #ifdef LGBCU_STAGE_TIMERS
-__device__ unsigned long long g_stage_cycles[16];
+__device__ unsigned long long g_stage_cycles[32];
 __device__ long long g_stage_prev;
 #define STAGE(i) do { if (blockIdx.x == 0 && blockIdx.y == 1 && threadIdx.x == 0) { long long t_ = clock64(); \
     g_stage_cycles[i] += (unsigned long long)(t_ - g_stage_prev); g_stage_prev = t_; } } while (0)
@@ -87,13 +87,17 @@ __device__ __forceinline__ int warp_argmax(double gain, unsigned tie, unsigned t
   bool a = valid;
   const unsigned m1 = __reduce_max_sync(FULL_MASK, a ? hi : 0u);
   a = a && hi == m1;
+  unsigned b = __ballot_sync(FULL_MASK, a);
+  if ((b & (b - 1)) == 0) return b ? __ffs(b) - 1 : -1;  // the high word alone decides (the usual case)
   const unsigned m2 = __reduce_max_sync(FULL_MASK, a ? lo : 0u);
   a = a && lo == m2;
+  b = __ballot_sync(FULL_MASK, a);
+  if ((b & (b - 1)) == 0) return __ffs(b) - 1;
   const unsigned m3 = __reduce_min_sync(FULL_MASK, a ? tie : 0xffffffffu);
   a = a && tie == m3;
   const unsigned m4 = __reduce_min_sync(FULL_MASK, a ? tie2 : 0xffffffffu);
   a = a && tie2 == m4;
-  const unsigned b = __ballot_sync(FULL_MASK, a);
+  b = __ballot_sync(FULL_MASK, a);
   return b ? __ffs(b) - 1 : -1;
 }
 
@@ -390,6 +394,7 @@ __device__ void scan_feature_block(ScanSmem& S, int nt, const DevFeat& F, double
       fb = cand_better(fb, c, false);
     }
   }
+  STAGE(20);
   rb = warp_best_cand(rb, true);
   fb = warp_best_cand(fb, false);
   splittable = __any_sync(FULL_MASK, splittable);
@@ -405,6 +410,7 @@ __device__ void scan_feature_block(ScanSmem& S, int nt, const DevFeat& F, double
     fb = warp_best_cand(y, false);
     splittable = __any_sync(FULL_MASK, sp);
   }
+  STAGE(21);
   if (tid != 0) return;
   const int any_split = splittable;
   // the winners' sums, formed exactly as the evaluating thread formed them
@@ -451,6 +457,7 @@ __device__ void scan_feature_block(ScanSmem& S, int nt, const DevFeat& F, double
   o.gain *= F.penalty;  // FindBestThreshold: output->gain *= meta_->penalty
   *out = o;
   *splittable_out = any_split;
+  STAGE(22);
 }
 
 // ComputeBestSplitForFeature (serial_tree_learner.cpp:709-718): the reference tests `leaf_index() == 0`, which holds
@@ -593,7 +600,7 @@ __device__ __forceinline__ SplitKey load_key_cg(const SplitKey* p) {
 }
 
 #ifdef LGBCU_STAGE_TIMERS
-#define CSTAGE(i) do { if (threadIdx.x == 0) { long long t_ = clock64(); g_stage_cycles[11 + (i)] += (unsigned long long)(t_ - ct_); ct_ = t_; } } while (0)
+#define CSTAGE(i) do { if (threadIdx.x == 0) { long long t_ = clock64(); g_stage_cycles[16 + (i)] += (unsigned long long)(t_ - ct_); ct_ = t_; } } while (0)
 #else
 #define CSTAGE(i) do {} while (0)
 #endif

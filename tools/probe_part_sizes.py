@@ -11,7 +11,7 @@ g = rng.standard_normal(n).astype(np.float32); h = np.full(n, 0.25, dtype=np.flo
 L = N.CudaLearner(); L.set_dataset(bins, metas)
 L.set_tree_params(N.make_tree_params(num_leaves=31, min_data_in_leaf=0, min_sum_hessian_in_leaf=1.0))
 L.set_gradients(g, h)
-o = (ctypes.c_ulonglong * 16)()
+o = (ctypes.c_ulonglong * 32)()
 for k in [2048, 8192, 32768, 131072, 524288, 2097152, 8388608]:
     bag = np.sort(rng.choice(n, size=k, replace=False)).astype(np.int32)
     res = []

@@ -19,14 +19,15 @@ L = N.CudaLearner(); L.set_dataset(bins, metas)
 L.set_tree_params(N.make_tree_params(num_leaves=leaves, min_data_in_leaf=0, min_sum_hessian_in_leaf=100.0))
 L.set_gradients(g, h)
 lib = N.lib
-out = (ctypes.c_ulonglong * 16)()
+out = (ctypes.c_ulonglong * 32)()
 for rep in range(3):
     L.begin_tree(); L.synchronize(); lib.lgbcu_debug_stages(out, 1)
     t0 = time.time(); recs = L.train_tree(); dt = time.time() - t0
     lib.lgbcu_debug_stages(out, 0)
     print(f"tree {dt*1e3:.2f} ms; find stages (us per call @1.9GHz): ", [round(out[i] / 1.9e3 / max(1, len(recs)), 2) for i in range(8)],
           " part stages [ctl+leaf, flags, barrier, prefix, scatter]:", [round(out[8 + i] / 1.9e3 / max(1, len(recs)), 2) for i in range(3)],
-          " control [prefetch, feature argmax+loads, leaf argmax, writes]:", [round(out[11 + i] / 1.9e3 / max(1, len(recs)), 2) for i in range(4)])
+          " control [prefetch, feature argmax+loads, leaf argmax, writes]:", [round(out[16 + i] / 1.9e3 / max(1, len(recs)), 2) for i in range(4)],
+          " gains [eval, reduce, epilogue]:", [round(out[20 + i] / 1.9e3 / max(1, len(recs)), 2) for i in range(3)])
 # per-split start stamps of the three kernels (graph path): deltas = kernel duration + gap
 ns = len(recs)
 st = (ctypes.c_ulonglong * (6 * ns))()
