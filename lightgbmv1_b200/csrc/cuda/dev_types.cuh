@@ -57,11 +57,34 @@ struct DevLeaf {     // DataPartition range + LeafSplits + pool slot of one leaf
   i64 tot_g, tot_h;     // exact fixed-point totals of the rows histogrammed into this leaf's slot
 };
 
+// Look-ahead growth.  The reference grows a tree best-first: split the open leaf with the largest gain, learn the
+// gains of its two children, repeat (serial_tree_learner.cpp:181-199).  Which leaves get split, and in which order, is
+// a function of the gains alone -- so the children of a leaf can be computed ("expanded": partition + histogram +
+// split search) BEFORE its turn comes without changing the result.  Every round expands the up to K open leaves with
+// the largest gains side by side (the kernels of a round are latency bound, so K leaves cost about as much as one),
+// then commits, in the reference's order, every leaf whose turn has come and whose children are ready.  An expansion
+// is only wasted if the leaf budget runs out before the leaf's turn.
+#define LGB_KMAX 8
+
+struct DevSpec {     // an expanded leaf that is not committed yet: what Split + two FindBestThreshold runs produced
+  DevLeaf child[2];  // [0] = left (keeps the parent's leaf id when committed), [1] = right (gets the next free id)
+  DevSplit best[2];  // best split of each child
+  SplitKey key[2];
+  int left_count;    // rows that went left on this rank
+  int smaller;       // which child got the freshly built histogram (the other one = parent - smaller)
+  int skip_find;     // BeforeFindBestSplit said no: the children cannot be split
+  int pad;
+};
+
 struct DevCtl {
   int num_leaves;    // leaves so far in the tree being grown
   int done;          // 1 once no leaf has positive gain / num_leaves reached
-  int smaller, larger;  // LeafSplits pair of serial_tree_learner (larger = -1 for the root)
-  int skip_find;     // BeforeFindBestSplit returned false
+  int smaller, larger;  // step-wise API only: LeafSplits pair of the last lgbcu_partition
+  int skip_find;     // BeforeFindBestSplit returned false (root round / step-wise API)
+  int lookahead;     // K: leaves expanded per round (1..LGB_KMAX)
+  int round;         // rounds run so far in this tree; round 0 = the root (histogram of leaf 0, search into best[0])
+  int num_items;     // leaves being expanded in the current round
+  int item_leaf[LGB_KMAX], item_feature[LGB_KMAX], item_threshold[LGB_KMAX], item_default_left[LGB_KMAX];
   int split_leaf, split_feature, split_threshold, split_default_left, split_right_leaf;
   int split_left_count;
   int num_splits;
@@ -71,8 +94,8 @@ struct DevCtl {
   int kg, kh;        // fixed-point exponents
   double scale_g, scale_h, inv_g, inv_h;
   unsigned feat_done;  // "last block done" counter of k_find_split
-  unsigned part_epoch;  // launches of k_partition so far (tags the words of V.part_sync); never reset
-  unsigned bar_arrive, bar_base;  // k_partition: blocks arrived so far (monotonic) / its value when this launch began
+  unsigned part_epoch[LGB_KMAX];  // per item: launches of k_partition so far (tags the words of V.part_sync); never reset
+  unsigned bar_arrive[LGB_KMAX], bar_base[LGB_KMAX];  // k_partition, per item: blocks arrived so far (monotonic) / value when the launch began
   long long global_root;  // root rows over all ranks   } adjacent: one 2 x int64 sum all-reduce
   long long global_rows;  // dataset rows over all ranks }
   unsigned long long prof_hist_rows, prof_hist_rows_indexed, prof_hist_calls, prof_hist_ns;
@@ -94,19 +117,24 @@ struct DevView {
   const DevFeat* feats;
   const int8_t* feat_used;   // ColSampler by-tree mask
   int8_t* splittable;        // [num_leaves slots][num_features]  FeatureHistogram::is_splittable_
-  int8_t* parent_split;      // [num_features] the split leaf's flags, snapshotted by k_part_scan for both children
+  int8_t* parent_split;      // [LGB_KMAX][num_features] the expanded leaves' flags, snapshotted by k_partition for their children
+  DevSpec* spec;             // [num_leaves] expansion results, indexed by the expanded leaf's id
+  int* expanded;             // [num_leaves] 1 = spec[leaf] holds a finished expansion that is not committed yet
+  int pool_slots;            // histogram slots in the pool
+  long long bits_stride;     // words of part_bits per item
   double2* mfb_fix;          // [num_leaves slots][num_features] FixHistogram'd most-frequent-bin entry, in double
   const float2* gh;          // interleaved (gradient, hessian) of the current iteration, written by k_absmax
   int* indices[2];
   HistEntry* pool;           // [num_leaves][total_bin]
   DevLeaf* leaves;
   DevSplit* best;            // best_split_per_leaf_
-  DevSplit* feat_best;       // [2][num_features] per-feature candidates of (smaller, larger)
-  SplitKey* feat_key;        // [2][num_features] (gain, real feature) of feat_best, 16 B each: coalesced arg-max
+  DevSplit* feat_best;       // [2 * LGB_KMAX][num_features] per-feature candidates of (smaller, larger) of every item
+  SplitKey* feat_key;        // [2 * LGB_KMAX][num_features] (gain, real feature) of feat_best, 16 B each: coalesced arg-max
   SplitKey* leaf_key;        // [num_leaves]      (gain, real feature) of best
   DevCtl* ctl;
   LgbCuSplitRecord* records;
-  unsigned long long* part_sync;  // partition scratch: (epoch << 32 | left count) per block
+  unsigned long long* part_sync;  // partition scratch: [LGB_KMAX][part_sync_stride] (epoch << 32 | left count) per block
+  int part_sync_stride;
   unsigned* part_bits;       // partition scratch: 1 bit per row (1 = goes left)
   DevParams p;
 };

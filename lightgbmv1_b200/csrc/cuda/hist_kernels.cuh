@@ -52,15 +52,6 @@ __device__ __forceinline__ void atomic_add_i64(i64* addr, i64 v) {
   atomicAdd(reinterpret_cast<unsigned long long*>(addr), (unsigned long long)v);
 }
 
-// Resolve which leaf a kernel works on: explicit (step-wise API) or the smaller leaf chosen on device.
-__device__ __forceinline__ bool hist_target(const DevView& V, int leaf_arg, int* leaf) {
-  if (leaf_arg >= 0) { *leaf = leaf_arg; return true; }
-  const DevCtl* c = V.ctl;
-  if (c->done || c->skip_find) return false;
-  *leaf = c->smaller;
-  return *leaf >= 0;
-}
-
 __device__ void hist_global_path(const DevView& V, const DevLeaf& L, bool identity, int bid, int nblocks) {
   const DevCtl* c = V.ctl;
   const double sg = c->scale_g, sh = c->scale_h;
@@ -91,7 +82,7 @@ __device__ void hist_global_path(const DevView& V, const DevLeaf& L, bool identi
 
 // smem: HIST_SMEM_BYTES of dynamic shared memory.  Called by all HIST_THREADS threads of every block.
 __device__ void hist_shared_path(const DevView& V, const DevLeaf& L, bool identity, int bid, int nblocks, int min_rows,
-                                 unsigned char* smem) {
+                                 int shift, unsigned char* smem) {
   const DevCtl* c = V.ctl;
   const double sg = c->scale_g, sh = c->scale_h;
   const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
@@ -112,7 +103,9 @@ __device__ void hist_shared_path(const DevView& V, const DevLeaf& L, bool identi
   namespace cg = cooperative_groups;
   cg::cluster_group cluster = cg::this_cluster();
   const int rank = (int)cluster.block_rank();
-  const int nclusters = nblocks / HIST_CLUSTER, cluster_id = bid / HIST_CLUSTER;
+  // `shift` rotates the cluster numbering so that the (few) units of different leaves of one round land on different
+  // clusters
+  const int nclusters = nblocks / HIST_CLUSTER, cluster_id = (bid / HIST_CLUSTER + nclusters - shift % nclusters) % nclusters;
   int PG = (L.count + HIST_CLUSTER * HIST_WARPS * min_rows - 1) / (HIST_CLUSTER * HIST_WARPS * min_rows);
   int cap = nclusters / NT; if (cap < 1) cap = 1;
   if (PG > cap) PG = cap;
@@ -237,27 +230,40 @@ __device__ void hist_shared_path(const DevView& V, const DevLeaf& L, bool identi
 }
 
 // mode: LGBCU_HIST_AUTO (by leaf size), LGBCU_HIST_GLOBAL_ATOMIC, LGBCU_HIST_WARP_PRIVATE (= the block-shared path)
-__device__ void hist_phase(const DevView& V, int leaf, int mode, int min_rows, int small_rows, int bid, int nblocks, unsigned char* smem) {
-  const DevLeaf L = V.leaves[leaf];
+__device__ void hist_phase(const DevView& V, const DevLeaf& L, bool is_root, int mode, int min_rows, int small_rows, int shift,
+                           int bid, int nblocks, unsigned char* smem) {
   const DevCtl* c = V.ctl;
-  const bool identity = c->root_identity && leaf == 0 && L.count == V.num_data;
+  const bool identity = c->root_identity && is_root && L.count == V.num_data;
   const bool small = mode == LGBCU_HIST_GLOBAL_ATOMIC || (mode == LGBCU_HIST_AUTO && L.count < small_rows);
   if (small) hist_global_path(V, L, identity, bid, nblocks);
-  else hist_shared_path(V, L, identity, bid, nblocks, min_rows, smem);
+  else hist_shared_path(V, L, identity, bid, nblocks, min_rows, shift, smem);
   if (bid == 0 && threadIdx.x == 0) {
     atomicAdd(&V.ctl->prof_hist_calls, 1ull);
     atomicAdd(identity ? &V.ctl->prof_hist_rows : &V.ctl->prof_hist_rows_indexed, (unsigned long long)L.count);
   }
 }
 
+// leaf_arg >= 0: that leaf (step-wise API).  leaf_arg < 0: training -- round 0 builds the root, every later round the
+// smaller child of each leaf being expanded (DevSpec); all of a round's leaves share this one launch.
 __global__ void __cluster_dims__(HIST_CLUSTER, 1, 1) __launch_bounds__(HIST_THREADS, HIST_BLOCKS_PER_SM) k_hist(DevView V, int leaf_arg, int mode, int min_rows, int small_rows) {
   extern __shared__ __align__(16) unsigned char hist_smem[];
-  int leaf;
+  const DevCtl* c = V.ctl;
   STAMP(V.ctl, 0);
-  if (!hist_target(V, leaf_arg, &leaf)) return;
-#ifdef LGBCU_STAGE_TIMERS
-  const int split_ = V.ctl->num_splits;
-#endif
-  hist_phase(V, leaf, mode, min_rows, small_rows, blockIdx.x, gridDim.x, hist_smem);
-  STAMP_END(split_, 0);
+  if (leaf_arg >= 0) {
+    hist_phase(V, V.leaves[leaf_arg], leaf_arg == 0, mode, min_rows, small_rows, 0, blockIdx.x, gridDim.x, hist_smem);
+    return;
+  }
+  if (c->done) return;
+  if (c->round == 0) {
+    if (!c->skip_find) hist_phase(V, V.leaves[0], true, mode, min_rows, small_rows, 0, blockIdx.x, gridDim.x, hist_smem);
+    return;
+  }
+  const int ni = c->num_items;
+  const int nclusters = (int)gridDim.x / HIST_CLUSTER;
+  for (int e = 0; e < ni; ++e) {
+    const DevSpec* S = &V.spec[c->item_leaf[e]];
+    if (S->skip_find) continue;
+    const DevLeaf L = S->child[S->smaller];
+    hist_phase(V, L, false, mode, min_rows, small_rows, e * (nclusters / ni), blockIdx.x, gridDim.x, hist_smem);
+  }
 }

@@ -123,6 +123,9 @@ struct LgbCuContext {
   // tree state
   DevParams params{}; bool params_set = false;
   int alloc_leaves = 0;
+  int lookahead = 4, alloc_lookahead = 0, pool_slots = 0, last_rounds = 0;  // K leaves expanded per round (LGBCU_LOOKAHEAD)
+  DevSpec* d_spec = nullptr; int* d_expanded = nullptr;
+  long long bits_stride = 0; int part_sync_stride = 0;
   HistEntry* d_pool = nullptr;
   int8_t* d_splittable = nullptr; int8_t* d_parent_split = nullptr; double2* d_mfb_fix = nullptr;
   DevLeaf* d_leaves = nullptr;
@@ -161,7 +164,8 @@ struct LgbCuContext {
     DevView V;
     V.num_data = N; V.num_features = F; V.row_stride = stride; V.total_bin = total_bin; V.num_tiles16 = ntiles16;
     V.bins = d_bins; V.feats = d_feats; V.feat_used = d_feat_used; V.splittable = d_splittable;
-    V.parent_split = d_parent_split; V.mfb_fix = d_mfb_fix;
+    V.parent_split = d_parent_split; V.mfb_fix = d_mfb_fix; V.spec = d_spec; V.expanded = d_expanded; V.pool_slots = pool_slots;
+    V.bits_stride = bits_stride; V.part_sync_stride = part_sync_stride;
     V.gh = d_gh; V.indices[0] = d_indices[0]; V.indices[1] = d_indices[1];
     V.pool = d_pool; V.leaves = d_leaves; V.best = d_best; V.feat_best = d_feat_best; V.feat_key = d_feat_key; V.leaf_key = d_leaf_key; V.ctl = d_ctl;
     V.records = d_records; V.part_sync = d_part_sync; V.bins_col = d_bins_col; V.col_stride = col_stride; V.part_bits = d_part_bits; V.p = params;
@@ -188,21 +192,34 @@ int ensure_tree_buffers(LgbCuContext* c) {
   NEED(c->F > 0 && c->N > 0, "lgbcu: dataset not set");
   NEED(c->params_set, "lgbcu: tree params not set");
   const int L = c->params.num_leaves;
-  if (c->alloc_leaves == L && c->d_pool) return 0;
+  if (c->alloc_leaves == L && c->alloc_lookahead == c->lookahead && c->d_pool) return 0;
   drop_graph(c);
   CU(cudaSetDevice(c->device));
-  CU(dev_alloc(&c->d_pool, (size_t)L * c->total_bin));
-  CU(dev_alloc(&c->d_splittable, (size_t)L * c->F));
-  CU(dev_alloc(&c->d_mfb_fix, (size_t)L * c->F));
-  CU(cudaMemsetAsync(c->d_mfb_fix, 0, sizeof(double2) * (size_t)L * c->F, c->stream));
+  // histogram slots: the root + one fresh slot per (round, item); a round commits at least one leaf, so there are at
+  // most L-1 rounds after the root.  Keep the pool under 1/8 of the device memory by lowering K if necessary.
+  {
+    size_t free_b = 0, total_b = 0;
+    CU(cudaMemGetInfo(&free_b, &total_b));
+    while (c->lookahead > 1 && (1 + (size_t)(L - 1) * c->lookahead) * c->total_bin * sizeof(HistEntry) > total_b / 8) c->lookahead -= 1;
+  }
+  const size_t slots = std::max<size_t>((size_t)L, 1 + (size_t)(L > 1 ? L - 1 : 0) * c->lookahead);
+  c->pool_slots = (int)slots;
+  CU(dev_alloc(&c->d_pool, slots * c->total_bin));
+  CU(dev_alloc(&c->d_splittable, slots * c->F));
+  CU(dev_alloc(&c->d_mfb_fix, slots * c->F));
+  CU(cudaMemsetAsync(c->d_mfb_fix, 0, sizeof(double2) * slots * c->F, c->stream));
   CU(dev_alloc(&c->d_leaves, (size_t)L));
   CU(dev_alloc(&c->d_best, (size_t)L));
   CU(dev_alloc(&c->d_leaf_key, (size_t)L));
+  CU(dev_alloc(&c->d_spec, (size_t)L));
+  CU(dev_alloc(&c->d_expanded, (size_t)L));
+  CU(cudaMemsetAsync(c->d_expanded, 0, sizeof(int) * (size_t)L, c->stream));
   CU(dev_alloc(&c->d_records, (size_t)L));
   CU(dev_alloc(&c->d_leaf_value, (size_t)L));
   if (c->h_records) cudaFreeHost(c->h_records);
   CU(cudaMallocHost(reinterpret_cast<void**>(&c->h_records), sizeof(LgbCuSplitRecord) * (size_t)L));
-  CU(cudaMemsetAsync(c->d_splittable, 0, (size_t)L * c->F, c->stream));
+  CU(cudaMemsetAsync(c->d_splittable, 0, slots * c->F, c->stream));
+  c->alloc_lookahead = c->lookahead;
   c->alloc_leaves = L;
   return 0;
 }
@@ -219,7 +236,14 @@ int launch_hist(LgbCuContext* c, int leaf_arg) {
 int launch_partition(LgbCuContext* c, long long rows, int mode) {
   const DevView V = c->view();
   cudaLaunchConfig_t cfg = {};
-  cfg.gridDim = dim3((unsigned)grid_for(c, rows, PART_TILE, c->part_blocks_per_sm) + 1u);
+  // training: the blocks are dealt to the round's items on the device; every item needs a tile block and a control block
+  unsigned grid = (unsigned)grid_for(c, rows, PART_TILE, c->part_blocks_per_sm) + 1u;
+  if (mode == 0) {
+    const unsigned cap = (unsigned)(c->num_sms * c->part_blocks_per_sm);
+    grid = std::min(cap, grid + 2u * (unsigned)c->lookahead);
+    grid = std::max(grid, 2u * (unsigned)c->lookahead);
+  }
+  cfg.gridDim = dim3(grid);
   cfg.blockDim = dim3(PART_THREADS);
   cfg.dynamicSmemBytes = 0;
   cfg.stream = c->stream;
@@ -245,10 +269,10 @@ int comm_allreduce_tree_setup(LgbCuContext* c) {
 
 // Split s builds the smaller leaf's histogram in pool slot s (slot 0 = root, then the fresh slot of split s
 // is s): known on the host without reading device state, so the collective can be enqueued blind.
-int comm_reduce_hist(LgbCuContext* c, int split_index) {
+int comm_reduce_hist(LgbCuContext* c, int first_slot, int num_slots) {
   if (!c->comm) return 0;
-  HistEntry* slot = c->d_pool + (size_t)split_index * c->total_bin;
-  NC(g_nccl.AllReduce(slot, slot, (size_t)c->total_bin * 2, ncclInt64, ncclSum, c->comm, c->stream));
+  HistEntry* slot = c->d_pool + (size_t)first_slot * c->total_bin;
+  NC(g_nccl.AllReduce(slot, slot, (size_t)c->total_bin * 2 * num_slots, ncclInt64, ncclSum, c->comm, c->stream));
   return 0;
 }
 
@@ -368,6 +392,7 @@ int lgbcu_create(int device_id, LgbCuContext** out) {
     // one slot per SM is left for the control block
     if (per_sm - 1 < c->part_blocks_per_sm) c->part_blocks_per_sm = per_sm - 1;
     if (const char* e = std::getenv("LGBCU_GRAPH")) c->use_graph = std::atoi(e) != 0;
+    if (const char* e = std::getenv("LGBCU_LOOKAHEAD")) { const int v = std::atoi(e); if (v >= 1 && v <= LGB_KMAX) c->lookahead = v; }
     if (const char* e = std::getenv("LGBCU_GRAPH_COMM")) c->graph_comm = std::atoi(e) != 0;
     if (const char* e = std::getenv("LGBCU_FORCE_DP_COUNTS")) c->force_dp_counts = std::atoi(e) != 0;
   }
@@ -386,7 +411,7 @@ int lgbcu_destroy(LgbCuContext* c) {
                   c->d_indices[0], c->d_indices[1], c->d_part_bits, c->d_part_sync, c->d_bins_col, c->d_query, c->d_label_gain,
                   c->d_inv_max_dcg, c->d_sigmoid_table, c->d_pool, c->d_splittable, c->d_leaves, c->d_best,
                   c->d_feat_best, c->d_ctl, c->d_records, c->d_leaf_value, c->d_export, c->d_tree_i32, c->d_tree_i8,
-                  c->d_tree_f64, c->d_rows, c->d_scratch, c->d_parent_split, c->d_mfb_fix, c->d_feat_key, c->d_leaf_key};
+                  c->d_tree_f64, c->d_rows, c->d_scratch, c->d_parent_split, c->d_mfb_fix, c->d_feat_key, c->d_leaf_key, c->d_spec, c->d_expanded};
   for (void* p : ptrs) if (p) cudaFree(p);
   if (c->h_records) cudaFreeHost(c->h_records);
   if (c->h_ctl) cudaFreeHost(c->h_ctl);
@@ -435,10 +460,10 @@ static int setup_dataset_common(LgbCuContext* c, int32_t num_data, int32_t num_f
   CU(dev_alloc(&c->d_bins_col, (size_t)c->col_stride * num_features));
   CU(dev_alloc(&c->d_feat_used, (size_t)num_features));
   CU(cudaMemsetAsync(c->d_feat_used, 1, num_features, c->stream));
-  CU(dev_alloc(&c->d_feat_best, (size_t)2 * num_features));
-  CU(dev_alloc(&c->d_feat_key, (size_t)2 * num_features));
-  CU(dev_alloc(&c->d_parent_split, (size_t)num_features));
-  CU(cudaMemsetAsync(c->d_parent_split, 1, num_features, c->stream));
+  CU(dev_alloc(&c->d_feat_best, (size_t)2 * LGB_KMAX * num_features));
+  CU(dev_alloc(&c->d_feat_key, (size_t)2 * LGB_KMAX * num_features));
+  CU(dev_alloc(&c->d_parent_split, (size_t)LGB_KMAX * num_features));
+  CU(cudaMemsetAsync(c->d_parent_split, 1, (size_t)LGB_KMAX * num_features, c->stream));
   CU(dev_alloc(&c->d_grad, (size_t)num_data));
   CU(dev_alloc(&c->d_hess, (size_t)num_data));
   CU(dev_alloc(&c->d_gh, (size_t)num_data));
@@ -447,9 +472,11 @@ static int setup_dataset_common(LgbCuContext* c, int32_t num_data, int32_t num_f
   CU(dev_alloc(&c->d_indices[0], (size_t)num_data));
   CU(dev_alloc(&c->d_indices[1], (size_t)num_data));
   const size_t ntiles = ((size_t)num_data + PART_TILE - 1) / PART_TILE;
-  CU(dev_alloc(&c->d_part_sync, (size_t)c->num_sms * 4 + 2));
-  CU(cudaMemset(c->d_part_sync, 0, sizeof(unsigned long long) * ((size_t)c->num_sms * 4 + 2)));
-  CU(dev_alloc(&c->d_part_bits, ntiles * (PART_TILE / 32)));
+  c->part_sync_stride = c->num_sms * 4 + 2;
+  CU(dev_alloc(&c->d_part_sync, (size_t)LGB_KMAX * c->part_sync_stride));
+  CU(cudaMemset(c->d_part_sync, 0, sizeof(unsigned long long) * (size_t)LGB_KMAX * c->part_sync_stride));
+  c->bits_stride = (long long)ntiles * (PART_TILE / 32);
+  CU(dev_alloc(&c->d_part_bits, (size_t)LGB_KMAX * c->bits_stride));
   CU(dev_alloc(&c->d_export, (size_t)2 * c->total_bin));
   c->alloc_leaves = 0;  // pool depends on total_bin
   drop_graph(c);
@@ -750,11 +777,11 @@ int lgbcu_begin_tree(LgbCuContext* c, const int32_t* bag_indices, int32_t bag_co
   } else {
     CU(cudaMemsetAsync(c->d_feat_used, 1, c->F, c->stream));
   }
-  CU(cudaMemsetAsync(c->d_pool, 0, sizeof(HistEntry) * (size_t)c->params.num_leaves * c->total_bin, c->stream));
+  CU(cudaMemsetAsync(c->d_pool, 0, sizeof(HistEntry) * (size_t)c->pool_slots * c->total_bin, c->stream));
   LAUNCH(k_reset_ctl_max, 1, 1, 0, c->stream, c->d_ctl, c->root_count, c->N);
   LAUNCH(k_absmax, grid_for(c, c->N, 256), 256, 0, c->stream, c->N, c->d_grad, c->d_hess, c->d_gh, c->d_ctl);
   if (comm_allreduce_tree_setup(c)) return -1;
-  LAUNCH(k_prepare_tree, 1, 256, 0, c->stream, c->view(), c->root_count, identity);
+  LAUNCH(k_prepare_tree, 1, 256, 0, c->stream, c->view(), c->root_count, identity, c->lookahead);
   CU(cudaGetLastError());
   if (bag_indices || feature_used) CU(cudaStreamSynchronize(c->stream));  // caller may reuse its buffers
   c->tree_begun = true;
@@ -884,27 +911,53 @@ int lgbcu_get_leaf_sums(LgbCuContext* c, int32_t leaf, double* sum_g, double* su
   return 0;
 }
 
+// One round of tree growth = {k_hist, [all-reduce], k_find_split (+ control), k_partition}.  Round 0 handles the root;
+// every later round expands up to K leaves and commits at least one (see DevSpec in dev_types.cuh).
+static int enqueue_round(LgbCuContext* c, int round, cudaEvent_t* ev) {
+  const DevView V = c->view();
+  const int K = c->lookahead;
+  if (ev) CU(cudaEventRecord(ev[0], c->stream));
+  if (launch_hist(c, -1)) return -1;
+  if (c->comm) {  // slots of a round are a function of (round, item): the collective is enqueued blind
+    const int first = round == 0 ? 0 : 1 + (round - 1) * K, count = round == 0 ? 1 : K;
+    if (first + count <= c->pool_slots && comm_reduce_hist(c, first, count)) return -1;
+  }
+  if (round == 0) LAUNCH(k_root_sums, 1, 32, 0, c->stream, V);
+  if (ev) CU(cudaEventRecord(ev[1], c->stream));
+  LAUNCH(k_find_split, dim3(c->F, 2 * K), FS_THREADS, 0, c->stream, V, 0, -1);
+  if (ev) CU(cudaEventRecord(ev[2], c->stream));
+  if (launch_partition(c, c->root_count, 0)) return -1;
+  if (ev) CU(cudaEventRecord(ev[3], c->stream));
+  return 0;
+}
+
 int lgbcu_train_tree(LgbCuContext* c, LgbCuSplitRecord* records, int32_t* num_splits) {
   NEED(c && records && num_splits, "lgbcu_train_tree: NULL argument");
   NEED(c->tree_begun, "lgbcu_train_tree: call lgbcu_begin_tree first");
   CU(cudaSetDevice(c->device));
-  const DevView V = c->view();
   const int L = c->params.num_leaves;
+  const int K = c->lookahead;
   const bool prof = c->profile;
+  const int max_rounds = L;  // the root round + at most L-1 rounds that commit one leaf each
+  // rounds enqueued before the host looks at `done` for the first time: what a tree needs when most expansions are
+  // committed in the round after they were made (measured: > 95 % on the benchmark workloads), plus some slack
+  int first_batch = 2 + ((L - 1) * 5 / 4 + K - 1) / K;
+  if (first_batch > max_rounds) first_batch = max_rounds;
+  int round = 0;
+  const int EV = 4;  // events per round: before hist, after hist (+ all-reduce), after find, after partition
+  if (prof && (int)c->ev.size() < EV * max_rounds) {
+    const size_t old = c->ev.size();
+    c->ev.resize(EV * max_rounds);
+    for (size_t i = old; i < c->ev.size(); ++i) CU(cudaEventCreate(&c->ev[i]));
+  }
   if (c->use_graph && !prof && (!c->comm || c->graph_comm)) {
-    // the launch sequence of a tree is fixed (all sizes are read on the device): capture it once, replay per tree
+    // the launch sequence of a batch of rounds is fixed (all sizes are read on the device): capture once, replay per tree
     if (!c->tree_graph) {
       cudaGraph_t g = nullptr;
       CU(cudaStreamBeginCapture(c->stream, cudaStreamCaptureModeThreadLocal));
       const long long before = g_launches.load(std::memory_order_relaxed);  // captured launches are not executions
       bool ok = true;
-      for (int s = 0; s < L - 1 && ok; ++s) {
-        ok = launch_hist(c, -1) == 0;
-        ok = ok && comm_reduce_hist(c, s) == 0;  // NCCL collectives are capturable: the all-reduce becomes a graph node
-        if (s == 0) LAUNCH(k_root_sums, 1, 32, 0, c->stream, V);
-        LAUNCH(k_find_split, dim3(c->F, 2), FS_THREADS, 0, c->stream, V, 0, -1);
-        ok = ok && launch_partition(c, c->root_count, 0) == 0;
-      }
+      for (int r = 0; r < first_batch && ok; ++r) ok = enqueue_round(c, r, nullptr) == 0;
       cudaError_t ce = cudaStreamEndCapture(c->stream, &g);
       g_launches.fetch_add(before - g_launches.load(std::memory_order_relaxed), std::memory_order_relaxed);
       if (!ok || ce != cudaSuccess || !g) { if (g) cudaGraphDestroy(g); return fail("lgbcu_train_tree: graph capture failed (%s)", cudaGetErrorString(ce)); }
@@ -913,70 +966,42 @@ int lgbcu_train_tree(LgbCuContext* c, LgbCuSplitRecord* records, int32_t* num_sp
       if (ce != cudaSuccess) { c->tree_graph = nullptr; return fail("lgbcu_train_tree: graph instantiate failed (%s)", cudaGetErrorString(ce)); }
     }
     CU(cudaGraphLaunch(c->tree_graph, c->stream));
-    g_launches.fetch_add((long long)(L - 1) * 3 + 1, std::memory_order_relaxed);
+    g_launches.fetch_add((long long)first_batch * 3 + 1, std::memory_order_relaxed);
+    round = first_batch;
+  } else {
+    for (; round < first_batch; ++round)
+      if (enqueue_round(c, round, prof ? &c->ev[EV * round] : nullptr)) return -1;
+  }
+  // look at the control block; a tree whose expansions were often not committed at once needs more rounds
+  while (true) {
+    CU(cudaGetLastError());
     CU(cudaMemcpyAsync(c->h_ctl, c->d_ctl, sizeof(DevCtl), cudaMemcpyDeviceToHost, c->stream));
-    CU(cudaMemcpyAsync(c->h_records, c->d_records, sizeof(LgbCuSplitRecord) * (size_t)(L - 1), cudaMemcpyDeviceToHost, c->stream));
     CU(cudaStreamSynchronize(c->stream));
-    const int n = c->h_ctl->num_splits;
-    NEED(n >= 0 && n <= L - 1, "lgbcu_train_tree: corrupt split count %d", n);
-    std::memcpy(records, c->h_records, sizeof(LgbCuSplitRecord) * (size_t)n);
-    *num_splits = n;
-    return 0;
+    if (c->h_ctl->done || round >= max_rounds) break;
+    for (int i = 0; i < 8 && round < max_rounds; ++i, ++round)
+      if (enqueue_round(c, round, prof ? &c->ev[EV * round] : nullptr)) return -1;
   }
-  // launch-per-phase loop (profiling, data-parallel, or graph disabled).  In profile mode every launch is bracketed
-  // by events so that per-phase device time (warm caches, real dependencies) can be reported.
-  const int EV = 6;  // events per split: before hist, after hist, after find, after flags, after scan, after scatter
-  if (prof && (int)c->ev.size() < EV * L) {
-    const size_t old = c->ev.size();
-    c->ev.resize(EV * L);
-    for (size_t i = old; i < c->ev.size(); ++i) CU(cudaEventCreate(&c->ev[i]));
-  }
-  for (int s = 0; s < L - 1; ++s) {
-    if (prof) CU(cudaEventRecord(c->ev[EV * s], c->stream));
-    if (launch_hist(c, -1)) return -1;
-    if (comm_reduce_hist(c, s)) return -1;
-    if (s == 0) LAUNCH(k_root_sums, 1, 32, 0, c->stream, V);
-    if (prof) CU(cudaEventRecord(c->ev[EV * s + 1], c->stream));
-    LAUNCH(k_find_split, dim3(c->F, 2), FS_THREADS, 0, c->stream, V, 0, -1);
-    if (prof) CU(cudaEventRecord(c->ev[EV * s + 2], c->stream));
-    if (launch_partition(c, c->root_count, 0)) return -1;  // flags + scan + scatter in one launch: reported as "flags"
-    if (prof) {
-      CU(cudaEventRecord(c->ev[EV * s + 3], c->stream));
-      CU(cudaEventRecord(c->ev[EV * s + 4], c->stream));
-      CU(cudaEventRecord(c->ev[EV * s + 5], c->stream));
-    }
-  }
-  CU(cudaGetLastError());
-  CU(cudaMemcpyAsync(c->h_ctl, c->d_ctl, sizeof(DevCtl), cudaMemcpyDeviceToHost, c->stream));
-  CU(cudaMemcpyAsync(c->h_records, c->d_records, sizeof(LgbCuSplitRecord) * (size_t)(L - 1), cudaMemcpyDeviceToHost, c->stream));
-  CU(cudaStreamSynchronize(c->stream));
+  NEED(c->h_ctl->done, "lgbcu_train_tree: tree not finished after %d rounds", round);
   const int n = c->h_ctl->num_splits;
   NEED(n >= 0 && n <= L - 1, "lgbcu_train_tree: corrupt split count %d", n);
-  std::memcpy(records, c->h_records, sizeof(LgbCuSplitRecord) * (size_t)n);
+  if (n > 0) {
+    CU(cudaMemcpyAsync(c->h_records, c->d_records, sizeof(LgbCuSplitRecord) * (size_t)n, cudaMemcpyDeviceToHost, c->stream));
+    CU(cudaStreamSynchronize(c->stream));
+    std::memcpy(records, c->h_records, sizeof(LgbCuSplitRecord) * (size_t)n);
+  }
   *num_splits = n;
+  c->last_rounds = round;
   if (prof) {
     for (int i = 0; i < 8; ++i) c->loop_phase_ms[i] = 0;
-    const int slot[5] = {0, 2, 4, 5, 6};  // hist, find(+control), flags, scan, scatter
-    for (int s = 0; s < L - 1; ++s) {
-      for (int k = 0; k < 5; ++k) {
-        float ms = 0; CU(cudaEventElapsedTime(&ms, c->ev[EV * s + k], c->ev[EV * s + k + 1]));
+    const int slot[3] = {0, 2, 4};  // hist (+ all-reduce), find + control, partition
+    for (int r = 0; r < round; ++r) {
+      for (int k = 0; k < 3; ++k) {
+        float ms = 0; CU(cudaEventElapsedTime(&ms, c->ev[EV * r + k], c->ev[EV * r + k + 1]));
         c->loop_phase_ms[slot[k]] += ms;
         if (k == 0) c->prof_hist_ms += ms;
       }
     }
     c->loop_phase_valid = true;
-    if (const char* path = std::getenv("LGBCU_PROF_DUMP")) {  // per-split phase times, for offline fitting
-      if (FILE* fp = std::fopen(path, "a")) {
-        for (int s = 0; s < n; ++s) {
-          float t[5];
-          for (int k = 0; k < 5; ++k) cudaEventElapsedTime(&t[k], c->ev[EV * s + k], c->ev[EV * s + k + 1]);
-          const int hist_rows = s == 0 ? c->root_count : std::min(records[s - 1].left_count, records[s - 1].right_count);
-          std::fprintf(fp, "%d,%d,%d,%.3f,%.3f,%.3f,%.3f,%.3f\n", s, hist_rows, records[s].left_count + records[s].right_count,
-                       t[0] * 1e3f, t[1] * 1e3f, t[2] * 1e3f, t[3] * 1e3f, t[4] * 1e3f);
-        }
-        std::fclose(fp);
-      }
-    }
   }
   return 0;
 }

@@ -79,7 +79,7 @@ __global__ void k_reset_ctl_max(DevCtl* ctl, int root_count, int num_data) {
 // BeforeTrain (src/treelearner/serial_tree_learner.cpp:244-272) on device: reset the control block, the
 // root leaf and the per-leaf best splits; derive the fixed-point scales from max|g|, max|h|.
 // scale_rows = number of rows a histogram entry can sum over (global row count in data-parallel mode).
-__global__ void k_prepare_tree(DevView V, int root_count, int root_identity) {
+__global__ void k_prepare_tree(DevView V, int root_count, int root_identity, int lookahead) {
   DevCtl* c = V.ctl;
   const long long scale_rows = c->global_rows;
   const int groot = (int)c->global_root;
@@ -94,12 +94,14 @@ __global__ void k_prepare_tree(DevView V, int root_count, int root_identity) {
     z.sum_g = z.sum_h = z.output = 0; z.tot_g = z.tot_h = 0;
     if (l == 0) { z.count = root_count; z.gcount = groot; }
     V.leaves[l] = z;
+    V.expanded[l] = 0;
   }
   if (threadIdx.x == 0) {
     c->num_leaves = 1; c->done = 0; c->smaller = 0; c->larger = -1;
     c->split_leaf = c->split_feature = c->split_threshold = 0;
     c->split_default_left = 0; c->split_right_leaf = 1; c->split_left_count = 0;
     c->num_splits = 0; c->feat_done = 0;
+    c->round = 0; c->num_items = 0; c->lookahead = lookahead;
     c->root_identity = root_identity; c->num_data = root_count;
     c->kg = fixed_exponent(c->max_g_bits, scale_rows);
     c->kh = fixed_exponent(c->max_h_bits, scale_rows);

@@ -60,8 +60,9 @@ __device__ __forceinline__ bool goes_left(const SplitRule& r, int bin) {
   return r.maxbin_left;
 }
 
-// The bookkeeping that follows a partition (one thread): leaf table, split record, smaller/larger, gates.
-__device__ void part_control(const DevView& V, int mode, int leaf, const DevLeaf& L, int left_cnt) {
+// The bookkeeping that follows a partition (one thread).
+// Step-wise API (lgbcu_partition): the children replace the leaf at once; sums are left to the caller.
+__device__ void part_control_stepwise(const DevView& V, int leaf, const DevLeaf& L, int left_cnt) {
   DevCtl* c = V.ctl;
   const int right_cnt = L.count - left_cnt;
   c->split_left_count = left_cnt;
@@ -70,13 +71,24 @@ __device__ void part_control(const DevView& V, int mode, int leaf, const DevLeaf
   A.count = left_cnt; A.buf = L.buf ^ 1; A.depth = L.depth + 1; A.gcount = left_cnt;
   B.begin = L.begin + left_cnt; B.count = right_cnt; B.buf = L.buf ^ 1; B.depth = L.depth + 1; B.gcount = right_cnt;
   A.tot_g = A.tot_h = B.tot_g = B.tot_h = 0;
-  if (mode == 1) {
-    B.slot = R;
-    V.leaves[leaf] = A;
-    V.leaves[R] = B;
-    if (c->num_leaves < R + 1) c->num_leaves = R + 1;
-    return;
-  }
+  B.slot = R;
+  V.leaves[leaf] = A;
+  V.leaves[R] = B;
+  if (c->num_leaves < R + 1) c->num_leaves = R + 1;
+}
+
+// Training: item e of the round expands leaf `leaf`.  The children (ranges, sums and outputs from the leaf's
+// SplitInfo as in SerialTreeLearner::SplitInner, serial_tree_learner.cpp:541-659; smaller / larger and the
+// histogram-pool hand-over, :298-312, 629-649; BeforeFindBestSplit gates, :274-297) go to spec[leaf]; the leaf
+// table is only touched when the expansion is committed (find_control).
+__device__ void part_expand(const DevView& V, int e, int leaf, const DevLeaf& L, int left_cnt) {
+  DevCtl* c = V.ctl;
+  DevSpec* S = &V.spec[leaf];
+  const int right_cnt = L.count - left_cnt;
+  DevLeaf A = L, B = L;  // A = left child, B = right child
+  A.count = left_cnt; A.buf = L.buf ^ 1; A.depth = L.depth + 1;
+  B.begin = L.begin + left_cnt; B.count = right_cnt; B.buf = L.buf ^ 1; B.depth = L.depth + 1;
+  A.tot_g = A.tot_h = B.tot_g = B.tot_h = 0;
   const DevSplit s = V.best[leaf];
   // SplitInner: on one GPU (update_cnt = true) the counts come from the partition; in data-parallel mode
   // (update_cnt = false, data_parallel_tree_learner.cpp:250-256) they stay the global, hessian-derived counts of
@@ -84,40 +96,19 @@ __device__ void part_control(const DevView& V, int mode, int leaf, const DevLeaf
   const int gl = V.data_parallel ? s.left_count : left_cnt;
   const int gr = V.data_parallel ? s.right_count : right_cnt;
   A.gcount = gl; B.gcount = gr;
-  LgbCuSplitRecord rec;
-  rec.leaf = leaf; rec.right_leaf = R; rec.feature = s.feature; rec.real_feature = s.real_feature;
-  rec.threshold = s.threshold; rec.default_left = s.default_left;
-  rec.left_count = gl; rec.right_count = gr;
-  rec.gain = (float)(s.gain + V.p.min_gain_to_split); rec.reserved = 0;
-  rec.left_output = s.left_output; rec.right_output = s.right_output;
-  rec.left_sum_hessian = s.left_sum_h; rec.right_sum_hessian = s.right_sum_h;
-  rec.left_sum_gradient = s.left_sum_g; rec.right_sum_gradient = s.right_sum_g;
-  V.records[c->num_splits] = rec;
-  c->num_splits += 1;
   A.sum_g = s.left_sum_g; A.sum_h = s.left_sum_h; A.output = s.left_output;
   B.sum_g = s.right_sum_g; B.sum_h = s.right_sum_h; B.output = s.right_output;
-  // smaller / larger (serial_tree_learner.cpp:629-649) and the histogram-pool hand-over (:298-312): the
-  // larger child inherits the parent's slot (subtraction happens in place), the smaller gets a fresh one.
-  int smaller, larger;
-  if (gl < gr) { smaller = leaf; larger = R; A.slot = R; B.slot = L.slot; }
-  else { smaller = R; larger = leaf; B.slot = R; A.slot = L.slot; }
-  V.leaves[leaf] = A;
-  V.leaves[R] = B;
-  c->smaller = smaller; c->larger = larger;
-  c->num_leaves = R + 1;
-  // BeforeFindBestSplit gates (serial_tree_learner.cpp:274-297)
+  // the larger child inherits the parent's slot (subtraction happens in place); the smaller one gets a fresh slot
+  // whose index depends on (round, item) only, so the host can address it blind (data-parallel all-reduce)
+  const int fresh = 1 + (c->round - 1) * c->lookahead + e;
+  int smaller;
+  if (gl < gr) { smaller = 0; A.slot = fresh; B.slot = L.slot; }
+  else { smaller = 1; B.slot = fresh; A.slot = L.slot; }
   int skip = 0;
   if (V.p.max_depth > 0 && A.depth >= V.p.max_depth) skip = 1;
   if (!skip && gr < V.p.min_data_in_leaf * 2 && gl < V.p.min_data_in_leaf * 2) skip = 1;
-  if (skip) {
-    V.best[leaf].gain = LGB_MIN_SCORE;
-    V.leaf_key[leaf].gain = LGB_MIN_SCORE;
-    DevSplit none; none.gain = LGB_MIN_SCORE; none.feature = -1; none.real_feature = -1;
-    V.best[R] = none;
-    { SplitKey k; k.gain = LGB_MIN_SCORE; k.real_feature = -1; k.pad = 0; V.leaf_key[R] = k; }
-  }
-  c->skip_find = skip;
-  if (c->num_leaves >= V.p.num_leaves) c->done = 2;  // tree is full; nothing more to enqueue
+  S->child[0] = A; S->child[1] = B;
+  S->left_count = left_cnt; S->smaller = smaller; S->skip_find = skip;
 }
 
 // ---------------------------------------------------------------------------------------------------------------
@@ -147,18 +138,47 @@ __global__ void __launch_bounds__(PART_THREADS, PART_BLOCKS_PER_SM + 1) k_partit
 #endif
   if (c->done) return;
   STAMP(c, 2);
-  const int leaf = c->split_leaf;
-  const unsigned epoch = c->part_epoch + 1u;  // every block reads these before it publishes; the control block
-  const unsigned bar_base = c->bar_base;      // updates them after all blocks have arrived
+  // which item (leaf being expanded) this block works for, and its index among that item's blocks
+  int e = 0, bid = blockIdx.x, maxp = (int)gridDim.x - 1;
+  int leaf = c->split_leaf, feature = c->split_feature, threshold = c->split_threshold, default_left = c->split_default_left;
+  if (mode == 0) {
+    const int ni = c->num_items;
+    if (ni <= 0) return;
+    // the grid's blocks are dealt to the items in proportion to their 1024-row tiles; one control block per item
+    int tiles[LGB_KMAX];
+    long long T = 0;
+#pragma unroll
+    for (int i = 0; i < LGB_KMAX; ++i) {
+      tiles[i] = 0;
+      if (i < ni) { tiles[i] = (V.leaves[c->item_leaf[i]].count + PART_TILE - 1) / PART_TILE; T += tiles[i]; }
+    }
+    const long long share = (long long)gridDim.x - 2 * ni;
+    int off = 0;
+    bool found = false;
+#pragma unroll
+    for (int i = 0; i < LGB_KMAX; ++i) {
+      if (i < ni && !found) {
+        int nb = (int)(T > 0 ? (long long)tiles[i] * share / T : 0);
+        if (nb < 1) nb = 1;
+        if (nb > tiles[i] && tiles[i] > 0) nb = tiles[i];
+        if ((int)blockIdx.x < off + nb + 1) { e = i; bid = (int)blockIdx.x - off; maxp = nb; found = true; }
+        off += nb + 1;
+      }
+    }
+    if (!found) return;
+    leaf = c->item_leaf[e]; feature = c->item_feature[e]; threshold = c->item_threshold[e]; default_left = c->item_default_left[e];
+  }
+  const unsigned epoch = c->part_epoch[e] + 1u;  // every block of the item reads these before it publishes; the item's
+  const unsigned bar_base = c->bar_base[e];      // control block updates them after all of them have arrived
   const DevLeaf L = V.leaves[leaf];
   const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
   const int ntiles = (L.count + PART_TILE - 1) / PART_TILE;
-  const int maxp = (int)gridDim.x - 1;
   const int tpb = (ntiles + maxp - 1) / maxp;          // tiles per block
   const int P = (ntiles + tpb - 1) / tpb;              // blocks that own tiles
-  const int bid = blockIdx.x;
   if (bid > P) return;
   const bool control = bid == P;
+  unsigned long long* psync = V.part_sync + (size_t)e * V.part_sync_stride;
+  unsigned* pbits = V.part_bits + (size_t)e * V.bits_stride;
   __shared__ unsigned s_bits[PART_SMEM_TILES][PART_TILE / 32];
   __shared__ int s_cnt[PART_THREADS / 32];
   __shared__ int s_red[2][PART_THREADS / 32];
@@ -169,13 +189,13 @@ __global__ void __launch_bounds__(PART_THREADS, PART_BLOCKS_PER_SM + 1) k_partit
   int row0[PART_REPS];  // rows of the block's first tile stay in registers for the scatter
   PSTAGE(0);
   if (!control) {
-    const DevFeat F = V.feats[c->split_feature];
-    const SplitRule rule = make_rule(F, c->split_threshold, c->split_default_left);
+    const DevFeat F = V.feats[feature];
+    const SplitRule rule = make_rule(F, threshold, default_left);
     // a large leaf holds a sizeable fraction of all rows, in ascending order: the column-major copy then serves many
     // rows per 32-byte sector; a small leaf touches one sector per row either way and the row-major read leaves
     // the row in L2 for the histogram pass that follows
     const bool by_column = (long long)L.count * PART_COLUMN_FRACTION >= V.num_data;
-    const uint8_t* col = by_column ? V.bins_col + (size_t)c->split_feature * V.col_stride : V.bins + c->split_feature;
+    const uint8_t* col = by_column ? V.bins_col + (size_t)feature * V.col_stride : V.bins + feature;
     const size_t rstride = by_column ? 1 : (size_t)V.row_stride;
     int lefts = 0;
     // the row indices of tile k+1 are in flight while the bins of tile k are gathered
@@ -208,7 +228,7 @@ __global__ void __launch_bounds__(PART_THREADS, PART_BLOCKS_PER_SM + 1) k_partit
         if (lane == 0) {
           const int wi = r * (PART_THREADS / 32) + warp;
           if (lt < PART_SMEM_TILES) s_bits[lt][wi] = word;
-          else V.part_bits[(size_t)tile * (PART_TILE / 32) + wi] = word;
+          else pbits[(size_t)tile * (PART_TILE / 32) + wi] = word;
           lefts += __popc(word);
         }
       }
@@ -219,21 +239,21 @@ __global__ void __launch_bounds__(PART_THREADS, PART_BLOCKS_PER_SM + 1) k_partit
     if (tid == 0) {
       int t = 0;
       for (int w = 0; w < PART_THREADS / 32; ++w) t += s_cnt[w];
-      *reinterpret_cast<volatile unsigned long long*>(&V.part_sync[bid]) = ((unsigned long long)epoch << 32) | (unsigned)t;
-      atomicAdd(&c->bar_arrive, 1u);
+      *reinterpret_cast<volatile unsigned long long*>(&psync[bid]) = ((unsigned long long)epoch << 32) | (unsigned)t;
+      atomicAdd(&c->bar_arrive[e], 1u);
     }
   }
   // one thread per block waits on the arrive counter (light polling); the words are then read once -- should one
   // not be visible yet (no fence orders it before the counter), its reader spins on the epoch tag
   if (tid == 0) {
-    while (*reinterpret_cast<volatile unsigned*>(&c->bar_arrive) - bar_base < (unsigned)P) { }
+    while (*reinterpret_cast<volatile unsigned*>(&c->bar_arrive[e]) - bar_base < (unsigned)P) { }
   }
   __syncthreads();
   // offsets: lefts of the blocks before this one, and of all blocks
   int before = 0, total = 0;
   for (int b = tid; b < P; b += PART_THREADS) {
     unsigned long long w;
-    do { w = *reinterpret_cast<volatile unsigned long long*>(&V.part_sync[b]); } while ((unsigned)(w >> 32) != epoch);
+    do { w = *reinterpret_cast<volatile unsigned long long*>(&psync[b]); } while ((unsigned)(w >> 32) != epoch);
     const int v = (int)(unsigned)w;
     total += v;
     if (b < bid) before += v;
@@ -255,16 +275,20 @@ __global__ void __launch_bounds__(PART_THREADS, PART_BLOCKS_PER_SM + 1) k_partit
   if (control) {
     if (mode == 0) {  // snapshot FeatureHistogram::is_splittable_ of the leaf being split for k_find_split
       const int8_t* sp = V.splittable + (size_t)L.slot * V.num_features;
-      for (int f = tid; f < V.num_features; f += PART_THREADS) V.parent_split[f] = sp[f];
+      for (int f = tid; f < V.num_features; f += PART_THREADS) V.parent_split[(size_t)e * V.num_features + f] = sp[f];
     }
-    if (tid == 0) { part_control(V, mode, leaf, L, total); c->part_epoch = epoch; c->bar_base = bar_base + (unsigned)P; }
+    if (tid == 0) {
+      if (mode == 1) part_control_stepwise(V, leaf, L, total);
+      else part_expand(V, e, leaf, L, total);
+      c->part_epoch[e] = epoch; c->bar_base[e] = bar_base + (unsigned)P;
+    }
     return;
   }
   const int left_total = total;
   int tile_off = before;
   for (int tile = t0; tile < t1; ++tile) {
     const int lt = tile - t0;
-    const unsigned myword = lt < PART_SMEM_TILES ? s_bits[lt][lane] : V.part_bits[(size_t)tile * (PART_TILE / 32) + lane];
+    const unsigned myword = lt < PART_SMEM_TILES ? s_bits[lt][lane] : pbits[(size_t)tile * (PART_TILE / 32) + lane];
     const int pc = __popc(myword);
     int inc = pc;
     for (int o = 1; o < 32; o <<= 1) {

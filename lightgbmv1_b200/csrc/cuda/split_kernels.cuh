@@ -480,19 +480,28 @@ __device__ __forceinline__ bool split_better(double ga, int fa, double gb, int f
 
 // FixHistogram / Subtract / FindBestThreshold of ONE (feature, leaf) pair by one block of FS_THREADS threads.
 // sel = 0: the smaller leaf; sel = 1: the larger leaf (= parent - smaller, formed here, in the parent's slot).
-__device__ void find_item(const DevView& V, ScanSmem& S, int f, int sel, int smaller, int larger) {
+// What one (feature, leaf) block of k_find_split works on.  The leaves are passed by value: in training they are the
+// not-yet-committed children of an expanded leaf (DevSpec), in the step-wise API an entry of the leaf table.
+struct FindTarget {
+  DevLeaf Ls, Ll;            // smaller leaf, larger leaf
+  int has_larger;            // 0: single leaf (root / step-wise)
+  int smaller_id0, larger_id0;  // the leaf carries id 0 (ComputeBestSplitForFeature's leaf_index() == 0 quirk)
+  int slot;                  // which (2 * item + sel) rows of feat_best / feat_key receive the results: slot + sel
+  const int8_t* parent_split;   // the expanded leaf's is_splittable flags (nullptr: none)
+};
+
+__device__ void find_item(const DevView& V, ScanSmem& S, int f, int sel, const FindTarget& T) {
   DevCtl* c = V.ctl;
   const int tid = threadIdx.x;
-  const int my_leaf = sel == 0 ? smaller : larger;
-  if (my_leaf < 0 || f >= V.num_features) return;
+  if ((sel == 1 && !T.has_larger) || f >= V.num_features) return;
   {
 
     const DevFeat F = V.feats[f];
-    const DevLeaf Ls = V.leaves[smaller];
+    const DevLeaf Ls = T.Ls;
     int used = V.feat_used[f] != 0;
     // a feature with no valid threshold in the parent is skipped in both children (serial_tree_learner.cpp:319-326);
     // k_part_scan snapshotted the parent's flags, so sibling blocks cannot race on them
-    if (larger >= 0) used = used && V.parent_split[f] != 0;
+    if (T.has_larger && T.parent_split) used = used && T.parent_split[f] != 0;
     const int nt = F.num_bin - F.offset;
     const double inv_g = c->inv_g, inv_h = c->inv_h;
     HistEntry* hs = V.pool + (size_t)Ls.slot * V.total_bin + F.hist_base;  // smaller leaf, slot 0 of the group
@@ -523,16 +532,16 @@ __device__ void find_item(const DevView& V, ScanSmem& S, int f, int sel, int sma
         }
         S.gi[tid] = e.g;
         __syncthreads();
-        scan_feature_block(S, nt, F, Ls.sum_g, Ls.sum_h, Ls.gcount, parent_output_of(Ls, smaller, V.p), V.p, inv_g, &o, &sp);
+        scan_feature_block(S, nt, F, Ls.sum_g, Ls.sum_h, Ls.gcount, parent_output_of(Ls, T.smaller_id0 ? 0 : 1, V.p), V.p, inv_g, &o, &sp);
         o.feature = f; o.real_feature = F.real_index;
       }
       if (tid == 0) {
-        V.feat_best[f] = o;
-        { SplitKey k; k.gain = o.gain; k.real_feature = o.real_feature; k.pad = o.feature >= 0 ? key_pack(o.feature, o.threshold, o.default_left) : 0; V.feat_key[f] = k; }
+        V.feat_best[(size_t)T.slot * V.num_features + f] = o;
+        { SplitKey k; k.gain = o.gain; k.real_feature = o.real_feature; k.pad = o.feature >= 0 ? key_pack(o.feature, o.threshold, o.default_left) : 0; V.feat_key[(size_t)T.slot * V.num_features + f] = k; }
         V.splittable[(size_t)Ls.slot * V.num_features + f] = (int8_t)sp;
       }
     } else {
-      const DevLeaf Ll = V.leaves[larger];
+      const DevLeaf Ll = T.Ll;
       if (used) {
         HistEntry* hl = V.pool + (size_t)Ll.slot * V.total_bin + F.hist_base;  // holds the parent
         double2* fix_l = V.mfb_fix + (size_t)Ll.slot * V.num_features + f;
@@ -569,12 +578,12 @@ __device__ void find_item(const DevView& V, ScanSmem& S, int f, int sel, int sma
         S.gi[tid] = e.g;
         __syncthreads();
         STAGE(1);
-        scan_feature_block(S, nt, F, Ll.sum_g, Ll.sum_h, Ll.gcount, parent_output_of(Ll, larger, V.p), V.p, inv_g, &o, &sp);
+        scan_feature_block(S, nt, F, Ll.sum_g, Ll.sum_h, Ll.gcount, parent_output_of(Ll, T.larger_id0 ? 0 : 1, V.p), V.p, inv_g, &o, &sp);
         o.feature = f; o.real_feature = F.real_index;
       }
       if (tid == 0) {
-        V.feat_best[V.num_features + f] = o;
-        { SplitKey k; k.gain = o.gain; k.real_feature = o.real_feature; k.pad = o.feature >= 0 ? key_pack(o.feature, o.threshold, o.default_left) : 0; V.feat_key[V.num_features + f] = k; }
+        V.feat_best[(size_t)(T.slot + 1) * V.num_features + f] = o;
+        { SplitKey k; k.gain = o.gain; k.real_feature = o.real_feature; k.pad = o.feature >= 0 ? key_pack(o.feature, o.threshold, o.default_left) : 0; V.feat_key[(size_t)(T.slot + 1) * V.num_features + f] = k; }
         if (used) V.splittable[(size_t)Ll.slot * V.num_features + f] = (int8_t)sp;
       }
     }
@@ -582,14 +591,17 @@ __device__ void find_item(const DevView& V, ScanSmem& S, int f, int sel, int sma
   __syncthreads();  // S is reused by the caller's next item
 }
 
-// Reduce the per-feature candidates of the two scanned leaves (SplitInfo::operator>), then pick the next leaf to
-// split (ArgMax over best_split_per_leaf_) and publish the split descriptor.  One warp.  Everything it compares is
-// read from the compact 16-byte key arrays with independent, coalesced loads (the per-leaf keys are prefetched
-// before the feature reduction).  A key also carries (inner feature, threshold, default_left) packed in `pad`, so the
-// descriptor of the winning split is known without fetching its 80-byte record; the records of the two scanned
-// leaves are copied feat_best -> best word-parallel by lanes 0..19, off the descriptor's critical path.
-#define CTRL_MAX_LEAF_KEYS 8   /* 32 lanes x 8 = 256 leaves prefetched; more are handled by a second pass */
+// ---- control step (last block of k_find_split) ---------------------------------------------------------------------
+// 1. reduce the per-feature candidates of every scanned leaf (SplitInfo::operator>) and store each leaf's best split
+//    (training: into the DevSpec of the leaf being expanded, which thereby becomes "expanded");
+// 2. commit, in the reference's order (ArgMax over best_split_per_leaf_, serial_tree_learner.cpp:181-199), every leaf
+//    whose turn has come and whose expansion is ready: its children enter the leaf table, the split record is written;
+// 3. choose the up to K open, not yet expanded leaves with the largest positive gains as the next round's items.
+// A key carries (inner feature, threshold, default_left) packed in `pad`, so an item's split descriptor is known
+// without fetching its 80-byte record.
 #define DEVSPLIT_WORDS ((int)(sizeof(DevSplit) / 4))
+#define DEVLEAF_WORDS ((int)(sizeof(DevLeaf) / 4))
+
 // L2 (cache-global) load of a SplitKey another block of this launch has just written: the last-block pattern orders
 // the writers (store, fence, ticket) -- the reader only has to bypass its own, non-coherent L1.
 __device__ __forceinline__ SplitKey load_key_cg(const SplitKey* p) {
@@ -598,145 +610,208 @@ __device__ __forceinline__ SplitKey load_key_cg(const SplitKey* p) {
   k.gain = __hiloint2double(v.y, v.x); k.real_feature = v.z; k.pad = v.w;
   return k;
 }
-
-#ifdef LGBCU_STAGE_TIMERS
-#define CSTAGE(i) do { if (threadIdx.x == 0) { long long t_ = clock64(); g_stage_cycles[16 + (i)] += (unsigned long long)(t_ - ct_); ct_ = t_; } } while (0)
-#else
-#define CSTAGE(i) do {} while (0)
-#endif
-__device__ void find_control(const DevView& V, int mode, bool active, int smaller, int larger,
-                             const SplitKey (*pre_key)[FS_WARPS], const int (*pre_idx)[FS_WARPS]) {
-  DevCtl* c = V.ctl;
-#ifdef LGBCU_STAGE_TIMERS
-  long long ct_ = clock64();
-#endif
-  const int lane = threadIdx.x & 31;
-  const int F = V.num_features;
-  const int nl = c->num_leaves;
-  // prefetch the keys of all current leaves (used by the final arg-max)
-  SplitKey lk[CTRL_MAX_LEAF_KEYS];
-#pragma unroll
-  for (int k = 0; k < CTRL_MAX_LEAF_KEYS; ++k) {
-    const int l = lane + 32 * k;
-    lk[k].gain = LGB_MIN_SCORE; lk[k].real_feature = -1; lk[k].pad = 0;
-    if (mode == 0 && l < nl) lk[k] = V.leaf_key[l];
-  }
-  CSTAGE(0);
-  SplitKey fresh[2];
-  int fresh_leaf[2] = {-1, -1};
-  int widx[2] = {-1, -1};
-  int wcopy[2] = {0, 0};
-  if (active) {
-    SplitKey fk[2];
-#pragma unroll
-    for (int sel = 0; sel < 2; ++sel) {  // both key loads are issued before either reduction
-      fk[sel].gain = LGB_MIN_SCORE; fk[sel].real_feature = -1; fk[sel].pad = 0;
-      const int leaf = sel == 0 ? smaller : larger;
-      if (!pre_key && leaf >= 0 && lane < F) fk[sel] = load_key_cg(&V.feat_key[sel * F + lane]);
-    }
-#pragma unroll
-    for (int sel = 0; sel < 2; ++sel) {
-      const int leaf = sel == 0 ? smaller : larger;
-      if (leaf < 0) continue;
-      double bg = LGB_MIN_SCORE; int bf = -1, bi = -1, bp = 0;
-      if (pre_key) {  // more than 32 features: the whole block has already reduced them to one candidate per warp
-        if (lane < FS_WARPS) { const SplitKey k = pre_key[sel][lane]; bg = k.gain; bf = k.real_feature; bp = k.pad; bi = pre_idx[sel][lane]; }
-      } else if (lane < F) {
-        bg = fk[sel].gain; bf = fk[sel].real_feature; bp = fk[sel].pad; bi = lane;
-      }
-      {  // (gain, feature) is a total order over distinct features: one winner
-        const unsigned tie = bf == -1 ? 0x7fffffffu : (unsigned)bf;
-        const int w = warp_argmax(bg, tie, 0u, bi >= 0 && bg == bg);
-        const int src = w < 0 ? 0 : w;
-        bg = __shfl_sync(FULL_MASK, bg, src); bf = __shfl_sync(FULL_MASK, bf, src);
-        bi = __shfl_sync(FULL_MASK, bi, src); bp = __shfl_sync(FULL_MASK, bp, src);
-        if (w < 0) {  // only NaN gains (or no feature at all): fall back to the first feature, as a sequential scan would
-          bi = F > 0 ? 0 : -1;
-          if (bi == 0) { const SplitKey k0 = load_key_cg(&V.feat_key[sel * F]); bg = k0.gain; bf = k0.real_feature; bp = k0.pad; }
-        }
-      }
-      widx[sel] = bi;
-      fresh_leaf[sel] = leaf;
-      fresh[sel].gain = bi >= 0 ? bg : LGB_MIN_SCORE;
-      fresh[sel].real_feature = bi >= 0 ? bf : -1;
-      fresh[sel].pad = bi >= 0 ? bp : 0;
-    }
-    // best_split_per_leaf_[leaf] = winner: 20 lanes move one 32-bit word each; the loads are issued here, the
-    // stores come last so that their latency hides behind the leaf arg-max
-#pragma unroll
-    for (int sel = 0; sel < 2; ++sel)
-      if (fresh_leaf[sel] >= 0 && widx[sel] >= 0 && lane < DEVSPLIT_WORDS)
-        wcopy[sel] = __ldcg(reinterpret_cast<const int*>(V.feat_best + (sel * F + widx[sel])) + lane);
-  }
-  CSTAGE(1);
-  auto finish_copies = [&]() {
-    if (!active) return;
-#pragma unroll
-    for (int sel = 0; sel < 2; ++sel) {
-      if (fresh_leaf[sel] < 0) continue;
-      if (widx[sel] >= 0) {
-        if (lane < DEVSPLIT_WORDS) reinterpret_cast<int*>(V.best + fresh_leaf[sel])[lane] = wcopy[sel];
-      } else if (lane == 0) {
-        DevSplit* r = V.best + fresh_leaf[sel];
-        r->gain = LGB_MIN_SCORE; r->feature = -1; r->real_feature = -1;
-      }
-      if (lane == 0) V.leaf_key[fresh_leaf[sel]] = fresh[sel];
-    }
-  };
-  if (mode != 0) { finish_copies(); return; }
-  // ArrayArgs<SplitInfo>::ArgMax(best_split_per_leaf_): first leaf with the best (gain, feature)
-  double bg = LGB_MIN_SCORE; int bf = -1, bl = -1, bp = 0;
-  auto consider = [&](int l, SplitKey k) {
-    if (l == fresh_leaf[0]) k = fresh[0];
-    if (l == fresh_leaf[1]) k = fresh[1];
-    if (bl < 0 || split_better(k.gain, k.real_feature, bg, bf)) { bg = k.gain; bf = k.real_feature; bl = l; bp = k.pad; }
-  };
-#pragma unroll
-  for (int k = 0; k < CTRL_MAX_LEAF_KEYS; ++k) {
-    const int l = lane + 32 * k;
-    if (l < nl) consider(l, lk[k]);
-  }
-  for (int l = lane + 32 * CTRL_MAX_LEAF_KEYS; l < nl; l += 32) consider(l, V.leaf_key[l]);
-  {  // first leaf with the best (gain, feature)
-    const unsigned tie = bf == -1 ? 0x7fffffffu : (unsigned)bf;
-    const int w = warp_argmax(bg, tie, (unsigned)bl, bl >= 0 && bg == bg);
-    const int src = w < 0 ? 0 : w;
-    bg = __shfl_sync(FULL_MASK, bg, src); bf = __shfl_sync(FULL_MASK, bf, src);
-    bl = __shfl_sync(FULL_MASK, bl, src); bp = __shfl_sync(FULL_MASK, bp, src);
-    if (w < 0) bl = -1;
-  }
-  CSTAGE(2);
-  if (lane == 0) {
-    if (bl < 0 || !(bg > 0.0)) {
-      c->done = 1;  // "No further splits with positive gain"
-    } else {
-      c->split_leaf = bl;
-      c->split_feature = bp & ((1 << KEY_FEAT_BITS) - 1);
-      c->split_threshold = (bp >> KEY_FEAT_BITS) & 511;
-      c->split_default_left = (bp >> (KEY_FEAT_BITS + 9)) & 1;
-      c->split_right_leaf = nl;
-    }
-  }
-  finish_copies();
-  CSTAGE(3);
+__device__ __forceinline__ void store_key(SplitKey* p, const SplitKey& k) {
+  int4 v;
+  v.x = __double2loint(k.gain); v.y = __double2hiint(k.gain); v.z = k.real_feature; v.w = k.pad;
+  *reinterpret_cast<int4*>(p) = v;
+}
+// one warp copies `nwords` 32-bit words (both ends 4-byte aligned, nwords <= 32)
+__device__ __forceinline__ void warp_copy_words(void* dst, const void* src, int nwords, int lane) {
+  if (lane < nwords) reinterpret_cast<int*>(dst)[lane] = __ldcg(reinterpret_cast<const int*>(src) + lane);
+}
+__device__ __forceinline__ SplitKey none_key() {
+  SplitKey k; k.gain = LGB_MIN_SCORE; k.real_feature = -1; k.pad = 0;
+  return k;
+}
+__device__ __forceinline__ void store_none_split(DevSplit* d, int lane) {
+  if (lane == 0) { d->gain = LGB_MIN_SCORE; d->feature = -1; d->real_feature = -1; }
 }
 
-// mode 0: training (smaller/larger from DevCtl, control step at the end);
-// mode 1: explicit single leaf, no control (step-wise API / tests).
-// grid = (num_features, 2): blockIdx.y = 0 scans the smaller leaf, 1 forms larger = parent - smaller and scans it.
+struct PairBest { double gain; int real_feature, idx, pad; };
+
+// all FS_THREADS threads: best (gain, feature) of row `p` of feat_key over the features -> one candidate per warp
+__device__ void reduce_feature_keys(const DevView& V, int p, PairBest* s_out /*[FS_WARPS]*/) {
+  const int F = V.num_features, lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+  double bg = LGB_MIN_SCORE; int bf = -1, bi = -1, bp = 0;
+  for (int j0 = threadIdx.x; j0 < F; j0 += 4 * FS_THREADS) {
+    SplitKey k[4];
+#pragma unroll
+    for (int u = 0; u < 4; ++u) {
+      const int j = j0 + u * FS_THREADS;
+      k[u] = none_key();
+      if (j < F) k[u] = load_key_cg(&V.feat_key[(size_t)p * F + j]);
+    }
+#pragma unroll
+    for (int u = 0; u < 4; ++u) {
+      const int j = j0 + u * FS_THREADS;
+      if (j < F && (bi < 0 || split_better(k[u].gain, k[u].real_feature, bg, bf))) {
+        bg = k[u].gain; bf = k[u].real_feature; bp = k[u].pad; bi = j;
+      }
+    }
+  }
+  const unsigned tie = bf == -1 ? 0x7fffffffu : (unsigned)bf;
+  int w = warp_argmax(bg, tie, 0u, bi >= 0 && bg == bg);
+  if (w < 0) w = __ffs(__ballot_sync(FULL_MASK, bi >= 0)) - 1;  // only NaN gains in this warp: its first feature
+  if (w < 0) w = 0;
+  PairBest r;
+  r.gain = __shfl_sync(FULL_MASK, bg, w); r.real_feature = __shfl_sync(FULL_MASK, bf, w);
+  r.idx = __shfl_sync(FULL_MASK, bi, w); r.pad = __shfl_sync(FULL_MASK, bp, w);
+  if (lane == 0) s_out[warp] = r;
+}
+
+// warp 0: combine the per-warp candidates of row p; returns the winner in every lane (idx < 0: no feature at all)
+__device__ PairBest combine_feature_keys(const PairBest* s_in /*[FS_WARPS]*/, int lane) {
+  PairBest c; c.gain = LGB_MIN_SCORE; c.real_feature = -1; c.idx = -1; c.pad = 0;
+  if (lane < FS_WARPS) c = s_in[lane];
+  const unsigned tie = c.real_feature == -1 ? 0x7fffffffu : (unsigned)c.real_feature;
+  int w = warp_argmax(c.gain, tie, 0u, c.idx >= 0 && c.gain == c.gain);
+  if (w < 0) w = __ffs(__ballot_sync(FULL_MASK, c.idx >= 0)) - 1;
+  PairBest r = c;
+  if (w < 0) { r.idx = -1; r.gain = LGB_MIN_SCORE; r.real_feature = -1; r.pad = 0; return r; }
+  r.gain = __shfl_sync(FULL_MASK, c.gain, w); r.real_feature = __shfl_sync(FULL_MASK, c.real_feature, w);
+  r.idx = __shfl_sync(FULL_MASK, c.idx, w); r.pad = __shfl_sync(FULL_MASK, c.pad, w);
+  return r;
+}
+
+// warp 0: store the winner of feat_best row p as the best split of one leaf
+__device__ void store_leaf_best(const DevView& V, int p, const PairBest& b, DevSplit* dst_split, SplitKey* dst_key, int lane) {
+  if (b.idx >= 0) warp_copy_words(dst_split, V.feat_best + ((size_t)p * V.num_features + b.idx), DEVSPLIT_WORDS, lane);
+  else store_none_split(dst_split, lane);
+  if (lane == 0) {
+    SplitKey k; k.gain = b.idx >= 0 ? b.gain : LGB_MIN_SCORE; k.real_feature = b.idx >= 0 ? b.real_feature : -1; k.pad = b.idx >= 0 ? b.pad : 0;
+    store_key(dst_key, k);
+  }
+}
+
+// warp 0: arg-max over the open leaves.  want_expanded < 0: all leaves; otherwise only leaves whose expanded flag
+// equals want_expanded and, if `taken` is given, that are not listed in it.  Returns (leaf, key) in every lane.
+__device__ int best_open_leaf(const DevView& V, int nl, int want_expanded, const int* taken, int ntaken, SplitKey* out, int lane) {
+  double bg = LGB_MIN_SCORE; int bf = -1, bl = -1, bp = 0;
+  for (int l = lane; l < nl; l += 32) {
+    if (want_expanded >= 0 && __ldcg(&V.expanded[l]) != want_expanded) continue;
+    bool skip = false;
+    for (int t = 0; t < ntaken; ++t) skip = skip || taken[t] == l;
+    if (skip) continue;
+    const SplitKey k = load_key_cg(&V.leaf_key[l]);
+    if (bl < 0 || split_better(k.gain, k.real_feature, bg, bf)) { bg = k.gain; bf = k.real_feature; bl = l; bp = k.pad; }
+  }
+  const unsigned tie = bf == -1 ? 0x7fffffffu : (unsigned)bf;
+  const int w = warp_argmax(bg, tie, (unsigned)bl, bl >= 0 && bg == bg);  // first leaf with the best (gain, feature)
+  if (w < 0) return -1;
+  out->gain = __shfl_sync(FULL_MASK, bg, w); out->real_feature = __shfl_sync(FULL_MASK, bf, w);
+  out->pad = __shfl_sync(FULL_MASK, bp, w);
+  return __shfl_sync(FULL_MASK, bl, w);
+}
+
+// warp 0: the expansion of `leaf` becomes part of the tree (SerialTreeLearner::SplitInner + Tree::Split bookkeeping)
+__device__ void commit_leaf(const DevView& V, int leaf, int lane) {
+  DevCtl* c = V.ctl;
+  const int R = c->num_leaves;
+  DevSpec* S = &V.spec[leaf];
+  if (lane == 0) {
+    const DevSplit s = V.best[leaf];  // the split that was applied
+    LgbCuSplitRecord rec;
+    rec.leaf = leaf; rec.right_leaf = R; rec.feature = s.feature; rec.real_feature = s.real_feature;
+    rec.threshold = s.threshold; rec.default_left = s.default_left;
+    rec.left_count = S->child[0].gcount; rec.right_count = S->child[1].gcount;
+    rec.gain = (float)(s.gain + V.p.min_gain_to_split); rec.reserved = 0;
+    rec.left_output = s.left_output; rec.right_output = s.right_output;
+    rec.left_sum_hessian = s.left_sum_h; rec.right_sum_hessian = s.right_sum_h;
+    rec.left_sum_gradient = s.left_sum_g; rec.right_sum_gradient = s.right_sum_g;
+    V.records[c->num_splits] = rec;
+  }
+  __syncwarp();
+  warp_copy_words(&V.leaves[leaf], &S->child[0], DEVLEAF_WORDS, lane);
+  warp_copy_words(&V.leaves[R], &S->child[1], DEVLEAF_WORDS, lane);
+  warp_copy_words(&V.best[leaf], &S->best[0], DEVSPLIT_WORDS, lane);
+  warp_copy_words(&V.best[R], &S->best[1], DEVSPLIT_WORDS, lane);
+  warp_copy_words(&V.leaf_key[leaf], &S->key[0], 4, lane);
+  warp_copy_words(&V.leaf_key[R], &S->key[1], 4, lane);
+  if (lane == 0) {
+    V.expanded[leaf] = 0; V.expanded[R] = 0;
+    c->num_splits += 1;
+    c->num_leaves = R + 1;
+  }
+  __threadfence_block();
+  __syncwarp();
+}
+
+// warp 0, training: steps 2 and 3 of the control step
+__device__ void commit_and_select(const DevView& V, int lane) {
+  DevCtl* c = V.ctl;
+  int nl = c->num_leaves;
+  const int max_leaves = V.p.num_leaves;
+  bool done = false;
+  SplitKey k;
+  // 2. commit
+  while (true) {
+    const int bl = best_open_leaf(V, nl, -1, nullptr, 0, &k, lane);
+    if (bl < 0 || !(k.gain > 0.0)) { done = true; if (lane == 0) c->done = 1; break; }  // "No further splits with positive gain"
+    if (__ldcg(&V.expanded[bl]) == 0) break;                                              // its children are not known yet
+    commit_leaf(V, bl, lane);
+    nl += 1;
+    if (nl >= max_leaves) { done = true; if (lane == 0) c->done = 2; break; }             // the tree is full
+  }
+  // 3. select the next round's items
+  int taken[LGB_KMAX];
+  int ni = 0;
+  if (!done) {
+    int K = c->lookahead;
+    if (K > max_leaves - nl) K = max_leaves - nl;
+    for (int e = 0; e < K; ++e) {
+      const int bl = best_open_leaf(V, nl, 0, taken, ni, &k, lane);
+      if (bl < 0 || !(k.gain > 0.0)) break;
+      taken[ni] = bl;
+      if (lane == 0) {
+        c->item_leaf[ni] = bl;
+        c->item_feature[ni] = k.pad & ((1 << KEY_FEAT_BITS) - 1);
+        c->item_threshold[ni] = (k.pad >> KEY_FEAT_BITS) & 511;
+        c->item_default_left[ni] = (k.pad >> (KEY_FEAT_BITS + 9)) & 1;
+      }
+      ++ni;
+    }
+  }
+  if (lane == 0) { c->num_items = ni; c->round += 1; }
+}
+
+// mode 0: training.  grid = (num_features, 2 * LGB_KMAX): blockIdx.y = 2 * item + sel; sel 0 scans the smaller child of
+//         the item's leaf, sel 1 forms larger = parent - smaller and scans it.  Round 0: only (item 0, sel 0) = root.
+// mode 1: one explicit leaf of the leaf table (step-wise API / tests), grid = (num_features, 1); result -> best[leaf].
 // The last block to finish runs the control step.
 __global__ void __launch_bounds__(FS_THREADS, 4) k_find_split(DevView V, int mode, int leaf_arg) {
   __shared__ ScanSmem S;
   __shared__ int s_last;
+  __shared__ PairBest s_pb[2 * LGB_KMAX][FS_WARPS];
   DevCtl* c = V.ctl;
   if (mode == 0 && c->done) return;
   STAGE_BEGIN();
   STAMP(c, 1);
-  const bool active = (mode == 1) || !c->skip_find;
-  const int smaller = (mode == 1) ? leaf_arg : c->smaller;
-  const int larger = (mode == 1) ? -1 : c->larger;
+  const int f = blockIdx.x, y = blockIdx.y, e = y >> 1, sel = y & 1;
+  const bool root_round = mode == 0 && c->round == 0;
+  const int ni = mode == 0 ? (root_round ? 1 : c->num_items) : 1;
+  FindTarget T;
+  bool active = false;
+  if (mode == 1 || root_round) {
+    if (y == 0 && (mode == 1 || !c->skip_find)) {
+      const int leaf = mode == 1 ? leaf_arg : 0;
+      T.Ls = V.leaves[leaf]; T.Ll = T.Ls; T.has_larger = 0; T.smaller_id0 = leaf == 0; T.larger_id0 = 0; T.slot = 0;
+      T.parent_split = nullptr;
+      active = true;
+    }
+  } else if (e < ni) {
+    const int parent = c->item_leaf[e];
+    const DevSpec* sp = &V.spec[parent];
+    if (!sp->skip_find) {
+      const int sm = sp->smaller;
+      T.Ls = sp->child[sm]; T.Ll = sp->child[1 - sm]; T.has_larger = 1;
+      // the left child keeps the parent's id, the right child gets a new id >= 1
+      T.smaller_id0 = parent == 0 && sm == 0; T.larger_id0 = parent == 0 && sm == 1;
+      T.slot = 2 * e; T.parent_split = V.parent_split + (size_t)e * V.num_features;
+      active = true;
+    }
+  }
   STAGE(0);
-  if (active) find_item(V, S, blockIdx.x, blockIdx.y, smaller, larger);
+  if (active) find_item(V, S, f, sel, T);
   STAGE(4);
   __threadfence();
   __syncthreads();
@@ -746,53 +821,42 @@ __global__ void __launch_bounds__(FS_THREADS, 4) k_find_split(DevView V, int mod
   }
   __syncthreads();
   STAGE(5);
-  STAMP_END(c->num_splits, 1);
   if (!s_last) return;
-  // More features than one warp covers: all 256 threads reduce the per-feature keys to one candidate per warp
-  // (independent, coalesced loads) before warp 0 runs the control step.
-  __shared__ SplitKey s_pk[2][FS_WARPS];
-  __shared__ int s_pi[2][FS_WARPS];
-  const bool wide = V.num_features > 32;
-  if (wide && active) {
-    const int F = V.num_features, lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
-#pragma unroll
-    for (int sel = 0; sel < 2; ++sel) {
-      const int leaf = sel == 0 ? smaller : larger;
-      double bg = LGB_MIN_SCORE; int bf = -1, bi = -1, bp = 0;
-      if (leaf >= 0) {
-        for (int j0 = threadIdx.x; j0 < F; j0 += 4 * FS_THREADS) {
-          SplitKey k[4];
-#pragma unroll
-          for (int u = 0; u < 4; ++u) {
-            const int j = j0 + u * FS_THREADS;
-            k[u].gain = LGB_MIN_SCORE; k[u].real_feature = -1; k[u].pad = 0;
-            if (j < F) k[u] = load_key_cg(&V.feat_key[sel * F + j]);
-          }
-#pragma unroll
-          for (int u = 0; u < 4; ++u) {
-            const int j = j0 + u * FS_THREADS;
-            if (j < F && (bi < 0 || split_better(k[u].gain, k[u].real_feature, bg, bf))) {
-              bg = k[u].gain; bf = k[u].real_feature; bp = k[u].pad; bi = j;
-            }
-          }
-        }
-      }
-      const unsigned tie = bf == -1 ? 0x7fffffffu : (unsigned)bf;
-      int w = warp_argmax(bg, tie, 0u, bi >= 0 && bg == bg);
-      if (w < 0) w = __ffs(__ballot_sync(FULL_MASK, bi >= 0)) - 1;  // only NaN gains in this warp: its first feature
-      if (w < 0) w = 0;
-      const double wg = __shfl_sync(FULL_MASK, bg, w);
-      const int wf = __shfl_sync(FULL_MASK, bf, w), wi = __shfl_sync(FULL_MASK, bi, w), wp = __shfl_sync(FULL_MASK, bp, w);
-      if (lane == 0) { SplitKey k; k.gain = wg; k.real_feature = wf; k.pad = wp; s_pk[sel][warp] = k; s_pi[sel][warp] = wi; }
-    }
-    __syncthreads();
-  }
+  // ---- control step, last block only
+  const int npairs = (mode == 1 || root_round) ? 1 : 2 * ni;
+  for (int p = 0; p < npairs; ++p) reduce_feature_keys(V, p, s_pb[p]);
+  __syncthreads();
   if (threadIdx.x >= 32) return;
 #ifdef LGBCU_STAGE_TIMERS
   long long tc0 = clock64();
 #endif
-  if (threadIdx.x == 0) c->feat_done = 0;
-  find_control(V, mode, active, smaller, larger, wide && active ? s_pk : nullptr, s_pi);
+  const int lane = threadIdx.x;
+  if (lane == 0) c->feat_done = 0;
+  if (mode == 1 || root_round) {
+    const int leaf = mode == 1 ? leaf_arg : 0;
+    if (mode == 1 || !c->skip_find) {
+      const PairBest b = combine_feature_keys(s_pb[0], lane);
+      store_leaf_best(V, 0, b, &V.best[leaf], &V.leaf_key[leaf], lane);
+    }
+  } else {
+    for (int i = 0; i < ni; ++i) {
+      const int parent = c->item_leaf[i];
+      DevSpec* sp = &V.spec[parent];
+      const int sm = sp->smaller;
+      if (sp->skip_find) {
+        for (int ch = 0; ch < 2; ++ch) { store_none_split(&sp->best[ch], lane); if (lane == 0) store_key(&sp->key[ch], none_key()); }
+      } else {
+        const PairBest b0 = combine_feature_keys(s_pb[2 * i], lane);
+        store_leaf_best(V, 2 * i, b0, &sp->best[sm], &sp->key[sm], lane);
+        const PairBest b1 = combine_feature_keys(s_pb[2 * i + 1], lane);
+        store_leaf_best(V, 2 * i + 1, b1, &sp->best[1 - sm], &sp->key[1 - sm], lane);
+      }
+      if (lane == 0) V.expanded[parent] = 1;
+    }
+  }
+  __threadfence_block();
+  __syncwarp();
+  if (mode == 0) commit_and_select(V, lane);
 #ifdef LGBCU_STAGE_TIMERS
   if (threadIdx.x == 0) { g_stage_cycles[6] += (unsigned long long)(clock64() - tc0); g_stage_cycles[7] += 1; }
 #endif
