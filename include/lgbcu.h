@@ -268,7 +268,8 @@ LGBCU_API int lgbcu_profile_read(LgbCuContext* ctx, double* hist_ms, int64_t* hi
                                  int reset);
 
 /* profile mode: milliseconds of the LAST tree spent in each phase (CUDA events around every launch of the
- * per-split sequence): [0] histogram (+ all-reduce) [2] split search + control [4] partition; other slots 0 */
+ * per-round sequence): [0] histogram (+ all-reduce) [2] split search + control [4] partition; [6] rounds enqueued for
+ * the last tree, [7] rounds it needed; other slots 0 */
 LGBCU_API int lgbcu_profile_phases(LgbCuContext* ctx, double* ms8);
 
 #ifdef __cplusplus

@@ -104,6 +104,8 @@ LGBM_B200_API int64_t LGBM_B200_LaunchCount(void);
 /* ours: histogram-kernel instrumentation of a booster (device ms, calls, algorithmic bytes); see lgbcu.h */
 LGBM_B200_API int LGBM_B200_BoosterProfile(BoosterHandle handle, int enable, int reset, double* hist_ms,
                                            int64_t* hist_calls, double* hist_bytes);
+/* profile mode: per-phase milliseconds and round counts of the last tree (lgbcu_profile_phases) */
+LGBM_B200_API int LGBM_B200_BoosterPhases(BoosterHandle handle, double* ms8);
 
 /* ours: introspection used by the parity tests (the reference exposes the same facts through
  * LGBM_DatasetDumpText, src/io/dataset.cpp:994-1044).  out_bins: [num_data][num_inner_features] BIN values

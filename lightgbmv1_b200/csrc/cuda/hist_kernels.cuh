@@ -82,7 +82,7 @@ __device__ void hist_global_path(const DevView& V, const DevLeaf& L, bool identi
 
 // smem: HIST_SMEM_BYTES of dynamic shared memory.  Called by all HIST_THREADS threads of every block.
 __device__ void hist_shared_path(const DevView& V, const DevLeaf& L, bool identity, int bid, int nblocks, int min_rows,
-                                 int shift, unsigned char* smem) {
+                                 unsigned char* smem) {
   const DevCtl* c = V.ctl;
   const double sg = c->scale_g, sh = c->scale_h;
   const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
@@ -103,9 +103,7 @@ __device__ void hist_shared_path(const DevView& V, const DevLeaf& L, bool identi
   namespace cg = cooperative_groups;
   cg::cluster_group cluster = cg::this_cluster();
   const int rank = (int)cluster.block_rank();
-  // `shift` rotates the cluster numbering so that the (few) units of different leaves of one round land on different
-  // clusters
-  const int nclusters = nblocks / HIST_CLUSTER, cluster_id = (bid / HIST_CLUSTER + nclusters - shift % nclusters) % nclusters;
+  const int nclusters = nblocks / HIST_CLUSTER, cluster_id = bid / HIST_CLUSTER;
   int PG = (L.count + HIST_CLUSTER * HIST_WARPS * min_rows - 1) / (HIST_CLUSTER * HIST_WARPS * min_rows);
   int cap = nclusters / NT; if (cap < 1) cap = 1;
   if (PG > cap) PG = cap;
@@ -230,13 +228,13 @@ __device__ void hist_shared_path(const DevView& V, const DevLeaf& L, bool identi
 }
 
 // mode: LGBCU_HIST_AUTO (by leaf size), LGBCU_HIST_GLOBAL_ATOMIC, LGBCU_HIST_WARP_PRIVATE (= the block-shared path)
-__device__ void hist_phase(const DevView& V, const DevLeaf& L, bool is_root, int mode, int min_rows, int small_rows, int shift,
+__device__ void hist_phase(const DevView& V, const DevLeaf& L, bool is_root, int mode, int min_rows, int small_rows,
                            int bid, int nblocks, unsigned char* smem) {
   const DevCtl* c = V.ctl;
   const bool identity = c->root_identity && is_root && L.count == V.num_data;
   const bool small = mode == LGBCU_HIST_GLOBAL_ATOMIC || (mode == LGBCU_HIST_AUTO && L.count < small_rows);
   if (small) hist_global_path(V, L, identity, bid, nblocks);
-  else hist_shared_path(V, L, identity, bid, nblocks, min_rows, shift, smem);
+  else hist_shared_path(V, L, identity, bid, nblocks, min_rows, smem);
   if (bid == 0 && threadIdx.x == 0) {
     atomicAdd(&V.ctl->prof_hist_calls, 1ull);
     atomicAdd(identity ? &V.ctl->prof_hist_rows : &V.ctl->prof_hist_rows_indexed, (unsigned long long)L.count);
@@ -250,20 +248,43 @@ __global__ void __cluster_dims__(HIST_CLUSTER, 1, 1) __launch_bounds__(HIST_THRE
   const DevCtl* c = V.ctl;
   STAMP(V.ctl, 0);
   if (leaf_arg >= 0) {
-    hist_phase(V, V.leaves[leaf_arg], leaf_arg == 0, mode, min_rows, small_rows, 0, blockIdx.x, gridDim.x, hist_smem);
+    hist_phase(V, V.leaves[leaf_arg], leaf_arg == 0, mode, min_rows, small_rows, blockIdx.x, gridDim.x, hist_smem);
     return;
   }
   if (c->done) return;
   if (c->round == 0) {
-    if (!c->skip_find) hist_phase(V, V.leaves[0], true, mode, min_rows, small_rows, 0, blockIdx.x, gridDim.x, hist_smem);
+    if (!c->skip_find) hist_phase(V, V.leaves[0], true, mode, min_rows, small_rows, blockIdx.x, gridDim.x, hist_smem);
     return;
   }
+  // The clusters of the grid are dealt to the round's leaves in proportion to their rows (at least one each), so
+  // that the leaves are histogrammed side by side; a cluster works for exactly one leaf.
   const int ni = c->num_items;
   const int nclusters = (int)gridDim.x / HIST_CLUSTER;
-  for (int e = 0; e < ni; ++e) {
-    const DevSpec* S = &V.spec[c->item_leaf[e]];
-    if (S->skip_find) continue;
-    const DevLeaf L = S->child[S->smaller];
-    hist_phase(V, L, false, mode, min_rows, small_rows, e * (nclusters / ni), blockIdx.x, gridDim.x, hist_smem);
+  const int my_cluster = (int)blockIdx.x / HIST_CLUSTER, rank = (int)blockIdx.x % HIST_CLUSTER;
+  long long rows[LGB_KMAX];
+  long long total = 0;
+  int live = 0;
+#pragma unroll
+  for (int e = 0; e < LGB_KMAX; ++e) {
+    rows[e] = 0;
+    if (e < ni) {
+      const DevSpec* S = &V.spec[c->item_leaf[e]];
+      if (!S->skip_find) { rows[e] = S->child[S->smaller].count > 0 ? S->child[S->smaller].count : 1; total += rows[e]; ++live; }
+    }
+  }
+  if (live == 0) return;
+  const int spare = nclusters - live;
+  int off = 0;
+#pragma unroll
+  for (int e = 0; e < LGB_KMAX; ++e) {
+    if (rows[e] == 0) continue;
+    const int nc = 1 + (int)(rows[e] * spare / total);
+    if (my_cluster >= off && my_cluster < off + nc) {
+      const DevSpec* S = &V.spec[c->item_leaf[e]];
+      const DevLeaf L = S->child[S->smaller];
+      hist_phase(V, L, false, mode, min_rows, small_rows, (my_cluster - off) * HIST_CLUSTER + rank, nc * HIST_CLUSTER, hist_smem);
+      return;
+    }
+    off += nc;
   }
 }

@@ -123,7 +123,7 @@ struct LgbCuContext {
   // tree state
   DevParams params{}; bool params_set = false;
   int alloc_leaves = 0;
-  int lookahead = 4, alloc_lookahead = 0, pool_slots = 0, last_rounds = 0;  // K leaves expanded per round (LGBCU_LOOKAHEAD)
+  int lookahead = LGB_KMAX, alloc_lookahead = 0, pool_slots = 0, last_rounds = 0;  // K leaves expanded per round (LGBCU_LOOKAHEAD)
   DevSpec* d_spec = nullptr; int* d_expanded = nullptr;
   long long bits_stride = 0; int part_sync_stride = 0;
   HistEntry* d_pool = nullptr;
@@ -1012,6 +1012,8 @@ int lgbcu_profile_phases(LgbCuContext* c, double* ms8) {
   CU(cudaMemcpyAsync(c->h_ctl, c->d_ctl, sizeof(DevCtl), cudaMemcpyDeviceToHost, c->stream));
   CU(cudaStreamSynchronize(c->stream));
   for (int i = 0; i < 8; ++i) ms8[i] = c->loop_phase_valid ? c->loop_phase_ms[i] : 0.0;
+  ms8[6] = (double)c->last_rounds;       // rounds enqueued for the last tree
+  ms8[7] = (double)c->h_ctl->round;      // rounds the tree actually needed (device counter)
   return 0;
 }
 

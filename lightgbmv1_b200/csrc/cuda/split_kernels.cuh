@@ -736,8 +736,8 @@ __device__ void commit_leaf(const DevView& V, int leaf, int lane) {
   __syncwarp();
 }
 
-// warp 0, training: steps 2 and 3 of the control step
-__device__ void commit_and_select(const DevView& V, int lane) {
+// warp 0, training: steps 2 and 3 of the control step -- general version, leaf keys re-read from memory every pass
+__device__ void commit_and_select_global(const DevView& V, int lane) {
   DevCtl* c = V.ctl;
   int nl = c->num_leaves;
   const int max_leaves = V.p.num_leaves;
@@ -762,6 +762,82 @@ __device__ void commit_and_select(const DevView& V, int lane) {
       const int bl = best_open_leaf(V, nl, 0, taken, ni, &k, lane);
       if (bl < 0 || !(k.gain > 0.0)) break;
       taken[ni] = bl;
+      if (lane == 0) {
+        c->item_leaf[ni] = bl;
+        c->item_feature[ni] = k.pad & ((1 << KEY_FEAT_BITS) - 1);
+        c->item_threshold[ni] = (k.pad >> KEY_FEAT_BITS) & 511;
+        c->item_default_left[ni] = (k.pad >> (KEY_FEAT_BITS + 9)) & 1;
+      }
+      ++ni;
+    }
+  }
+  if (lane == 0) { c->num_items = ni; c->round += 1; }
+}
+
+// warp 0, training: steps 2 and 3 of the control step for trees of up to 256 leaves -- every lane keeps the keys and
+// expanded flags of its 8 leaves (leaf = lane + 32 * slot) in registers, so a pass is 8 local compares and one warp
+// arg-max; a commit patches the two registers it changes.
+#define CTRL_SLOTS 8
+__device__ void commit_and_select(const DevView& V, int lane) {
+  DevCtl* c = V.ctl;
+  const int max_leaves = V.p.num_leaves;
+  if (max_leaves > 32 * CTRL_SLOTS) { commit_and_select_global(V, lane); return; }
+  int nl = c->num_leaves;
+  SplitKey key[CTRL_SLOTS];
+  int ex[CTRL_SLOTS];
+  unsigned taken = 0;  // bit per slot: chosen as an item of the next round
+#pragma unroll
+  for (int k = 0; k < CTRL_SLOTS; ++k) {
+    const int l = lane + 32 * k;
+    key[k] = none_key(); ex[k] = 0;
+    if (l < nl) { key[k] = load_key_cg(&V.leaf_key[l]); ex[k] = __ldcg(&V.expanded[l]); }
+  }
+  // arg-max over the open leaves; want < 0: all, else only leaves with expanded flag == want that are not taken
+  auto best = [&](int want, SplitKey* out, int* out_ex) -> int {
+    double bg = LGB_MIN_SCORE; int bf = -1, bl = -1, bp = 0, be = 0;
+#pragma unroll
+    for (int k = 0; k < CTRL_SLOTS; ++k) {
+      const int l = lane + 32 * k;
+      if (l >= nl) continue;
+      if (want >= 0 && (ex[k] != want || ((taken >> k) & 1u))) continue;
+      if (bl < 0 || split_better(key[k].gain, key[k].real_feature, bg, bf)) {
+        bg = key[k].gain; bf = key[k].real_feature; bl = l; bp = key[k].pad; be = ex[k];
+      }
+    }
+    const unsigned tie = bf == -1 ? 0x7fffffffu : (unsigned)bf;
+    const int w = warp_argmax(bg, tie, (unsigned)bl, bl >= 0 && bg == bg);  // first leaf with the best (gain, feature)
+    if (w < 0) return -1;
+    out->gain = __shfl_sync(FULL_MASK, bg, w); out->real_feature = __shfl_sync(FULL_MASK, bf, w);
+    out->pad = __shfl_sync(FULL_MASK, bp, w);
+    *out_ex = __shfl_sync(FULL_MASK, be, w);
+    return __shfl_sync(FULL_MASK, bl, w);
+  };
+  bool done = false;
+  SplitKey k; int kex = 0;
+  while (true) {
+    const int bl = best(-1, &k, &kex);
+    if (bl < 0 || !(k.gain > 0.0)) { done = true; if (lane == 0) c->done = 1; break; }  // "No further splits with positive gain"
+    if (kex == 0) break;                                                                  // its children are not known yet
+    const SplitKey k0 = load_key_cg(&V.spec[bl].key[0]), k1 = load_key_cg(&V.spec[bl].key[1]);
+    commit_leaf(V, bl, lane);
+    const int R = nl;
+#pragma unroll
+    for (int s = 0; s < CTRL_SLOTS; ++s) {
+      if (lane + 32 * s == bl) { key[s] = k0; ex[s] = 0; }
+      if (lane + 32 * s == R) { key[s] = k1; ex[s] = 0; }
+    }
+    nl += 1;
+    if (nl >= max_leaves) { done = true; if (lane == 0) c->done = 2; break; }             // the tree is full
+  }
+  int ni = 0;
+  if (!done) {
+    int K = c->lookahead;
+    if (K > max_leaves - nl) K = max_leaves - nl;
+    for (int e = 0; e < K; ++e) {
+      const int bl = best(0, &k, &kex);
+      if (bl < 0 || !(k.gain > 0.0)) break;
+#pragma unroll
+      for (int s = 0; s < CTRL_SLOTS; ++s) if (lane + 32 * s == bl) taken |= 1u << s;
       if (lane == 0) {
         c->item_leaf[ni] = bl;
         c->item_feature[ni] = k.pad & ((1 << KEY_FEAT_BITS) - 1);

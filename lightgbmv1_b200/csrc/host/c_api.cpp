@@ -283,6 +283,13 @@ int LGBM_B200_BoosterProfile(BoosterHandle handle, int enable, int reset, double
   API_END();
 }
 
+int LGBM_B200_BoosterPhases(BoosterHandle handle, double* ms8) {
+  API_BEGIN();
+  LgbCuContext* ctx = reinterpret_cast<Booster*>(handle)->gbdt->device();
+  if (lgbcu_profile_phases(ctx, ms8) != 0) Log::Fatal("%s", lgbcu_last_error());
+  API_END();
+}
+
 int LGBM_B200_DatasetNumInnerFeatures(DatasetHandle handle, int* out) {
   API_BEGIN();
   *out = reinterpret_cast<Dataset*>(handle)->num_features();

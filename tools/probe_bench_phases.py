@@ -1,0 +1,19 @@
+"""Scratch probe: per-phase time and round counts of one boosting iteration of bench.py's workload (profile mode)."""
+import os, sys, ctypes as C
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+sys.path.insert(0, ROOT); sys.path.insert(0, os.path.join(ROOT, "tests"))
+import numpy as np
+import bench, capi
+ours = capi.ours(); lib = ours.lib
+X, y = bench.higgs_shaped(bench.N_ROWS)
+ds = ours.dataset_from_mat(X, bench.PARAMS); ours.set_field(ds, "label", y)
+b = ours.booster_create(ds, bench.PARAMS)
+for _ in range(3): ours.update(b)
+ms, calls, nb = C.c_double(), C.c_int64(), C.c_double()
+ours.check(lib.LGBM_B200_BoosterProfile(b, 1, 1, C.byref(ms), C.byref(calls), C.byref(nb)))
+ph = (C.c_double * 8)()
+for _ in range(3):
+    ours.update(b)
+    ours.check(lib.LGBM_B200_BoosterPhases(b, ph))
+    print("K=%s phases ms: hist %.2f find+control %.2f partition %.2f; rounds enqueued %d used %d" % (
+        os.environ.get("LGBCU_LOOKAHEAD", "default"), ph[0], ph[2], ph[4], ph[6], ph[7]))
