@@ -64,7 +64,7 @@ struct DevLeaf {     // DataPartition range + LeafSplits + pool slot of one leaf
 // the largest gains side by side (the kernels of a round are latency bound, so K leaves cost about as much as one),
 // then commits, in the reference's order, every leaf whose turn has come and whose children are ready.  An expansion
 // is only wasted if the leaf budget runs out before the leaf's turn.
-#define LGB_KMAX 8
+#define LGB_KMAX 16
 
 struct DevSpec {     // an expanded leaf that is not committed yet: what Split + two FindBestThreshold runs produced
   DevLeaf child[2];  // [0] = left (keeps the parent's leaf id when committed), [1] = right (gets the next free id)

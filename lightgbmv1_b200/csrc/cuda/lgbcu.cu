@@ -777,7 +777,8 @@ int lgbcu_begin_tree(LgbCuContext* c, const int32_t* bag_indices, int32_t bag_co
   } else {
     CU(cudaMemsetAsync(c->d_feat_used, 1, c->F, c->stream));
   }
-  CU(cudaMemsetAsync(c->d_pool, 0, sizeof(HistEntry) * (size_t)c->pool_slots * c->total_bin, c->stream));
+  // only the root's slot: every later slot is zeroed by the partition launch that hands it out
+  CU(cudaMemsetAsync(c->d_pool, 0, sizeof(HistEntry) * (size_t)c->total_bin, c->stream));
   LAUNCH(k_reset_ctl_max, 1, 1, 0, c->stream, c->d_ctl, c->root_count, c->N);
   LAUNCH(k_absmax, grid_for(c, c->N, 256), 256, 0, c->stream, c->N, c->d_grad, c->d_hess, c->d_gh, c->d_ctl);
   if (comm_allreduce_tree_setup(c)) return -1;
@@ -941,7 +942,7 @@ int lgbcu_train_tree(LgbCuContext* c, LgbCuSplitRecord* records, int32_t* num_sp
   const int max_rounds = L;  // the root round + at most L-1 rounds that commit one leaf each
   // rounds enqueued before the host looks at `done` for the first time: what a tree needs when most expansions are
   // committed in the round after they were made (measured: > 95 % on the benchmark workloads), plus some slack
-  int first_batch = 2 + ((L - 1) * 5 / 4 + K - 1) / K;
+  int first_batch = 2 + ((L - 1) * 8 / 5 + K - 1) / K;
   if (first_batch > max_rounds) first_batch = max_rounds;
   int round = 0;
   const int EV = 4;  // events per round: before hist, after hist (+ all-reduce), after find, after partition

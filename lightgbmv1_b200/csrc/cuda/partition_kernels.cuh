@@ -277,6 +277,12 @@ __global__ void __launch_bounds__(PART_THREADS, PART_BLOCKS_PER_SM + 1) k_partit
       const int8_t* sp = V.splittable + (size_t)L.slot * V.num_features;
       for (int f = tid; f < V.num_features; f += PART_THREADS) V.parent_split[(size_t)e * V.num_features + f] = sp[f];
     }
+    if (mode == 0) {  // the fresh histogram slot of this expansion (see part_expand) must be zero before k_hist adds to it
+      const int fresh = 1 + (c->round - 1) * c->lookahead + e;
+      uint4* z = reinterpret_cast<uint4*>(V.pool + (size_t)fresh * V.total_bin);
+      const uint4 zero = make_uint4(0, 0, 0, 0);
+      for (int i = tid; i < V.total_bin; i += PART_THREADS) z[i] = zero;
+    }
     if (tid == 0) {
       if (mode == 1) part_control_stepwise(V, leaf, L, total);
       else part_expand(V, e, leaf, L, total);

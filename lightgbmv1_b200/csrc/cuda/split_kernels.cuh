@@ -629,21 +629,21 @@ __device__ __forceinline__ void store_none_split(DevSplit* d, int lane) {
 
 struct PairBest { double gain; int real_feature, idx, pad; };
 
-// all FS_THREADS threads: best (gain, feature) of row `p` of feat_key over the features -> one candidate per warp
-__device__ void reduce_feature_keys(const DevView& V, int p, PairBest* s_out /*[FS_WARPS]*/) {
-  const int F = V.num_features, lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+// one warp: best (gain, feature) of row `p` of feat_key over all features; result in every lane (idx < 0: none)
+__device__ PairBest warp_reduce_feature_keys(const DevView& V, int p, int lane) {
+  const int F = V.num_features;
   double bg = LGB_MIN_SCORE; int bf = -1, bi = -1, bp = 0;
-  for (int j0 = threadIdx.x; j0 < F; j0 += 4 * FS_THREADS) {
+  for (int j0 = lane; j0 < F; j0 += 4 * 32) {
     SplitKey k[4];
 #pragma unroll
     for (int u = 0; u < 4; ++u) {
-      const int j = j0 + u * FS_THREADS;
+      const int j = j0 + u * 32;
       k[u] = none_key();
       if (j < F) k[u] = load_key_cg(&V.feat_key[(size_t)p * F + j]);
     }
 #pragma unroll
     for (int u = 0; u < 4; ++u) {
-      const int j = j0 + u * FS_THREADS;
+      const int j = j0 + u * 32;
       if (j < F && (bi < 0 || split_better(k[u].gain, k[u].real_feature, bg, bf))) {
         bg = k[u].gain; bf = k[u].real_feature; bp = k[u].pad; bi = j;
       }
@@ -651,29 +651,15 @@ __device__ void reduce_feature_keys(const DevView& V, int p, PairBest* s_out /*[
   }
   const unsigned tie = bf == -1 ? 0x7fffffffu : (unsigned)bf;
   int w = warp_argmax(bg, tie, 0u, bi >= 0 && bg == bg);
-  if (w < 0) w = __ffs(__ballot_sync(FULL_MASK, bi >= 0)) - 1;  // only NaN gains in this warp: its first feature
-  if (w < 0) w = 0;
-  PairBest r;
+  if (w < 0) w = __ffs(__ballot_sync(FULL_MASK, bi >= 0)) - 1;  // only NaN gains: the first feature
+  PairBest r; r.gain = LGB_MIN_SCORE; r.real_feature = -1; r.idx = -1; r.pad = 0;
+  if (w < 0) return r;
   r.gain = __shfl_sync(FULL_MASK, bg, w); r.real_feature = __shfl_sync(FULL_MASK, bf, w);
   r.idx = __shfl_sync(FULL_MASK, bi, w); r.pad = __shfl_sync(FULL_MASK, bp, w);
-  if (lane == 0) s_out[warp] = r;
-}
-
-// warp 0: combine the per-warp candidates of row p; returns the winner in every lane (idx < 0: no feature at all)
-__device__ PairBest combine_feature_keys(const PairBest* s_in /*[FS_WARPS]*/, int lane) {
-  PairBest c; c.gain = LGB_MIN_SCORE; c.real_feature = -1; c.idx = -1; c.pad = 0;
-  if (lane < FS_WARPS) c = s_in[lane];
-  const unsigned tie = c.real_feature == -1 ? 0x7fffffffu : (unsigned)c.real_feature;
-  int w = warp_argmax(c.gain, tie, 0u, c.idx >= 0 && c.gain == c.gain);
-  if (w < 0) w = __ffs(__ballot_sync(FULL_MASK, c.idx >= 0)) - 1;
-  PairBest r = c;
-  if (w < 0) { r.idx = -1; r.gain = LGB_MIN_SCORE; r.real_feature = -1; r.pad = 0; return r; }
-  r.gain = __shfl_sync(FULL_MASK, c.gain, w); r.real_feature = __shfl_sync(FULL_MASK, c.real_feature, w);
-  r.idx = __shfl_sync(FULL_MASK, c.idx, w); r.pad = __shfl_sync(FULL_MASK, c.pad, w);
   return r;
 }
 
-// warp 0: store the winner of feat_best row p as the best split of one leaf
+// one warp: store the winner of feat_best row p as the best split of one leaf
 __device__ void store_leaf_best(const DevView& V, int p, const PairBest& b, DevSplit* dst_split, SplitKey* dst_key, int lane) {
   if (b.idx >= 0) warp_copy_words(dst_split, V.feat_best + ((size_t)p * V.num_features + b.idx), DEVSPLIT_WORDS, lane);
   else store_none_split(dst_split, lane);
@@ -704,6 +690,31 @@ __device__ int best_open_leaf(const DevView& V, int nl, int want_expanded, const
 }
 
 // warp 0: the expansion of `leaf` becomes part of the tree (SerialTreeLearner::SplitInner + Tree::Split bookkeeping)
+// one warp: expansion of `leaf` -> leaf table, with the right child's id R and the record index given
+__device__ void commit_leaf_as(const DevView& V, int leaf, int R, int record_index, int lane) {
+  DevSpec* S = &V.spec[leaf];
+  if (lane == 0) {
+    const DevSplit s = V.best[leaf];  // the split that was applied
+    LgbCuSplitRecord rec;
+    rec.leaf = leaf; rec.right_leaf = R; rec.feature = s.feature; rec.real_feature = s.real_feature;
+    rec.threshold = s.threshold; rec.default_left = s.default_left;
+    rec.left_count = S->child[0].gcount; rec.right_count = S->child[1].gcount;
+    rec.gain = (float)(s.gain + V.p.min_gain_to_split); rec.reserved = 0;
+    rec.left_output = s.left_output; rec.right_output = s.right_output;
+    rec.left_sum_hessian = s.left_sum_h; rec.right_sum_hessian = s.right_sum_h;
+    rec.left_sum_gradient = s.left_sum_g; rec.right_sum_gradient = s.right_sum_g;
+    V.records[record_index] = rec;
+  }
+  __syncwarp();
+  warp_copy_words(&V.leaves[leaf], &S->child[0], DEVLEAF_WORDS, lane);
+  warp_copy_words(&V.leaves[R], &S->child[1], DEVLEAF_WORDS, lane);
+  warp_copy_words(&V.best[leaf], &S->best[0], DEVSPLIT_WORDS, lane);
+  warp_copy_words(&V.best[R], &S->best[1], DEVSPLIT_WORDS, lane);
+  warp_copy_words(&V.leaf_key[leaf], &S->key[0], 4, lane);
+  warp_copy_words(&V.leaf_key[R], &S->key[1], 4, lane);
+  if (lane == 0) { V.expanded[leaf] = 0; V.expanded[R] = 0; }
+}
+
 __device__ void commit_leaf(const DevView& V, int leaf, int lane) {
   DevCtl* c = V.ctl;
   const int R = c->num_leaves;
@@ -774,14 +785,16 @@ __device__ void commit_and_select_global(const DevView& V, int lane) {
   if (lane == 0) { c->num_items = ni; c->round += 1; }
 }
 
-// warp 0, training: steps 2 and 3 of the control step for trees of up to 256 leaves -- every lane keeps the keys and
-// expanded flags of its 8 leaves (leaf = lane + 32 * slot) in registers, so a pass is 8 local compares and one warp
-// arg-max; a commit patches the two registers it changes.
+// warp 0, training, trees of up to 256 leaves: DECIDE steps 2 and 3 of the control step without touching the leaf
+// table.  Every lane keeps the keys and expanded flags of its 8 leaves (leaf = lane + 32 * slot) in registers, so a
+// pass is 8 local compares and one warp arg-max; the children's keys of every expanded leaf were staged in shared
+// memory (s_ck) by the whole block.  Output: the leaves to commit, in order (s_commit, *s_nc) -- the copies are then
+// done by all warps in parallel -- plus the next round's items and the done flag in DevCtl.
 #define CTRL_SLOTS 8
-__device__ void commit_and_select(const DevView& V, int lane) {
+#define CTRL_MAX_LEAVES (32 * CTRL_SLOTS)
+__device__ void plan_commits(const DevView& V, int lane, const SplitKey (*s_ck)[2], int* s_commit, int* s_nc) {
   DevCtl* c = V.ctl;
   const int max_leaves = V.p.num_leaves;
-  if (max_leaves > 32 * CTRL_SLOTS) { commit_and_select_global(V, lane); return; }
   int nl = c->num_leaves;
   SplitKey key[CTRL_SLOTS];
   int ex[CTRL_SLOTS];
@@ -812,22 +825,23 @@ __device__ void commit_and_select(const DevView& V, int lane) {
     *out_ex = __shfl_sync(FULL_MASK, be, w);
     return __shfl_sync(FULL_MASK, bl, w);
   };
-  bool done = false;
+  int done = 0, nc = 0;
   SplitKey k; int kex = 0;
   while (true) {
     const int bl = best(-1, &k, &kex);
-    if (bl < 0 || !(k.gain > 0.0)) { done = true; if (lane == 0) c->done = 1; break; }  // "No further splits with positive gain"
-    if (kex == 0) break;                                                                  // its children are not known yet
-    const SplitKey k0 = load_key_cg(&V.spec[bl].key[0]), k1 = load_key_cg(&V.spec[bl].key[1]);
-    commit_leaf(V, bl, lane);
+    if (bl < 0 || !(k.gain > 0.0)) { done = 1; break; }  // "No further splits with positive gain"
+    if (kex == 0) break;                                  // its children are not known yet
+    const SplitKey k0 = s_ck[bl][0], k1 = s_ck[bl][1];
     const int R = nl;
+    if (lane == 0) s_commit[nc] = bl;
+    ++nc;
 #pragma unroll
     for (int s = 0; s < CTRL_SLOTS; ++s) {
       if (lane + 32 * s == bl) { key[s] = k0; ex[s] = 0; }
       if (lane + 32 * s == R) { key[s] = k1; ex[s] = 0; }
     }
     nl += 1;
-    if (nl >= max_leaves) { done = true; if (lane == 0) c->done = 2; break; }             // the tree is full
+    if (nl >= max_leaves) { done = 2; break; }            // the tree is full
   }
   int ni = 0;
   if (!done) {
@@ -847,7 +861,7 @@ __device__ void commit_and_select(const DevView& V, int lane) {
       ++ni;
     }
   }
-  if (lane == 0) { c->num_items = ni; c->round += 1; }
+  if (lane == 0) { c->num_items = ni; c->round += 1; if (done) c->done = done; *s_nc = nc; }
 }
 
 // mode 0: training.  grid = (num_features, 2 * LGB_KMAX): blockIdx.y = 2 * item + sel; sel 0 scans the smaller child of
@@ -857,7 +871,6 @@ __device__ void commit_and_select(const DevView& V, int lane) {
 __global__ void __launch_bounds__(FS_THREADS, 4) k_find_split(DevView V, int mode, int leaf_arg) {
   __shared__ ScanSmem S;
   __shared__ int s_last;
-  __shared__ PairBest s_pb[2 * LGB_KMAX][FS_WARPS];
   DevCtl* c = V.ctl;
   if (mode == 0 && c->done) return;
   STAGE_BEGIN();
@@ -898,41 +911,57 @@ __global__ void __launch_bounds__(FS_THREADS, 4) k_find_split(DevView V, int mod
   __syncthreads();
   STAGE(5);
   if (!s_last) return;
-  // ---- control step, last block only
-  const int npairs = (mode == 1 || root_round) ? 1 : 2 * ni;
-  for (int p = 0; p < npairs; ++p) reduce_feature_keys(V, p, s_pb[p]);
-  __syncthreads();
-  if (threadIdx.x >= 32) return;
+  // ---- control step, last block only.  Step 1: every warp reduces feat_key rows (one leaf each) and stores that
+  // leaf's best split where it belongs.
+  __shared__ SplitKey s_ck[CTRL_MAX_LEAVES][2];
+  __shared__ int s_commit[CTRL_MAX_LEAVES];
+  __shared__ int s_nc;
+  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
 #ifdef LGBCU_STAGE_TIMERS
   long long tc0 = clock64();
 #endif
-  const int lane = threadIdx.x;
-  if (lane == 0) c->feat_done = 0;
+  if (threadIdx.x == 0) c->feat_done = 0;
   if (mode == 1 || root_round) {
     const int leaf = mode == 1 ? leaf_arg : 0;
-    if (mode == 1 || !c->skip_find) {
-      const PairBest b = combine_feature_keys(s_pb[0], lane);
+    if (warp == 0 && (mode == 1 || !c->skip_find)) {
+      const PairBest b = warp_reduce_feature_keys(V, 0, lane);
       store_leaf_best(V, 0, b, &V.best[leaf], &V.leaf_key[leaf], lane);
     }
   } else {
-    for (int i = 0; i < ni; ++i) {
-      const int parent = c->item_leaf[i];
-      DevSpec* sp = &V.spec[parent];
-      const int sm = sp->smaller;
+    for (int p = warp; p < 2 * ni; p += FS_WARPS) {
+      const int i = p >> 1, which = p & 1;  // which = 0: the smaller child's row, 1: the larger child's
+      DevSpec* sp = &V.spec[c->item_leaf[i]];
+      const int child = which == 0 ? sp->smaller : 1 - sp->smaller;
       if (sp->skip_find) {
-        for (int ch = 0; ch < 2; ++ch) { store_none_split(&sp->best[ch], lane); if (lane == 0) store_key(&sp->key[ch], none_key()); }
+        store_none_split(&sp->best[child], lane);
+        if (lane == 0) store_key(&sp->key[child], none_key());
       } else {
-        const PairBest b0 = combine_feature_keys(s_pb[2 * i], lane);
-        store_leaf_best(V, 2 * i, b0, &sp->best[sm], &sp->key[sm], lane);
-        const PairBest b1 = combine_feature_keys(s_pb[2 * i + 1], lane);
-        store_leaf_best(V, 2 * i + 1, b1, &sp->best[1 - sm], &sp->key[1 - sm], lane);
+        const PairBest b = warp_reduce_feature_keys(V, p, lane);
+        store_leaf_best(V, p, b, &sp->best[child], &sp->key[child], lane);
       }
-      if (lane == 0) V.expanded[parent] = 1;
     }
   }
   __threadfence_block();
-  __syncwarp();
-  if (mode == 0) commit_and_select(V, lane);
+  __syncthreads();
+  if (mode == 1) return;
+  if (!root_round && threadIdx.x < ni) V.expanded[c->item_leaf[threadIdx.x]] = 1;
+  __threadfence_block();
+  __syncthreads();
+  const int nl0 = c->num_leaves, ns0 = c->num_splits;
+  if (V.p.num_leaves > CTRL_MAX_LEAVES) {  // big trees: the general, sequential version
+    if (warp == 0) commit_and_select_global(V, lane);
+    return;
+  }
+  // steps 2 and 3: stage the children's keys of every expanded leaf, let warp 0 decide, then all warps copy
+  for (int l = threadIdx.x; l < nl0; l += FS_THREADS) {
+    if (__ldcg(&V.expanded[l])) { s_ck[l][0] = load_key_cg(&V.spec[l].key[0]); s_ck[l][1] = load_key_cg(&V.spec[l].key[1]); }
+  }
+  __syncthreads();
+  if (warp == 0) plan_commits(V, lane, s_ck, s_commit, &s_nc);
+  __syncthreads();
+  const int nc = s_nc;
+  for (int i = warp; i < nc; i += FS_WARPS) commit_leaf_as(V, s_commit[i], nl0 + i, ns0 + i, lane);
+  if (threadIdx.x == 0) { c->num_leaves = nl0 + nc; c->num_splits = ns0 + nc; }
 #ifdef LGBCU_STAGE_TIMERS
   if (threadIdx.x == 0) { g_stage_cycles[6] += (unsigned long long)(clock64() - tc0); g_stage_cycles[7] += 1; }
 #endif
