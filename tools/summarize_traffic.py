@@ -20,6 +20,6 @@ out = {"source": src, "launches": len(ids), "dram_bytes_read": rd, "dram_bytes_w
        "dram_bytes_per_launch": (rd + wr) / len(ids), "ncu_time_ms": ns / 1e6,
        "root_launch": {"dram_bytes": root["dram__bytes_read.sum"] + root["dram__bytes_write.sum"],
                        "ncu_time_us": root["gpu__time_duration.sum"] / 1e3},
-       "note": "one tree (254 launches) of bench.py's workload; ncu flushes caches between launches, so these are cold numbers"}
+       "note": "the rounds of one tree of bench.py workload"}
 json.dump(out, open(dst, "w"), indent=1)
 print(json.dumps(out, indent=1))
