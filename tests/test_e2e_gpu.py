@@ -201,3 +201,21 @@ def test_errors_surface_through_last_error():
         ours.booster_create(ds, "objective=binary boosting=dart")
     with pytest.raises(capi.LGBMError):
         ours.set_field(ds, "label", y[:10])
+
+
+def test_more_than_256_leaves_uses_the_general_control_path():
+    # trees of more than 256 leaves take the sequential commit/select path of the control step
+    X, y = higgs_like(21, 60_000)
+    params = "objective=binary num_leaves=400 min_data_in_leaf=5 min_sum_hessian_in_leaf=1e-3 learning_rate=0.1 verbosity=-1"
+    ref, ours, br, bo, nr, no = run_both(X, y, params, 3)
+    assert_same_model(ref, ours, br, bo)
+
+
+@pytest.mark.parametrize("lookahead", ["1", "3", "16"])
+def test_model_does_not_depend_on_the_lookahead(lookahead, monkeypatch):
+    # look-ahead growth expands leaves early but commits them in the reference's order: any K gives the same trees
+    X, y = higgs_like(22, 80_000)
+    params = "objective=binary num_leaves=63 min_data_in_leaf=20 learning_rate=0.1 max_depth=9 verbosity=-1"
+    monkeypatch.setenv("LGBCU_LOOKAHEAD", lookahead)
+    ref, ours, br, bo, nr, no = run_both(X, y, params, 5)
+    assert_same_model(ref, ours, br, bo)
