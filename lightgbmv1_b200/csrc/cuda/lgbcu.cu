@@ -1003,6 +1003,16 @@ int lgbcu_train_tree(LgbCuContext* c, LgbCuSplitRecord* records, int32_t* num_sp
       }
     }
     c->loop_phase_valid = true;
+    if (const char* path = std::getenv("LGBCU_PROF_DUMP")) {  // per-round phase times (us), for offline analysis
+      if (FILE* fp = std::fopen(path, "a")) {
+        for (int r = 0; r < round; ++r) {
+          float t[3];
+          for (int k = 0; k < 3; ++k) cudaEventElapsedTime(&t[k], c->ev[EV * r + k], c->ev[EV * r + k + 1]);
+          std::fprintf(fp, "%d,%.2f,%.2f,%.2f\n", r, t[0] * 1e3f, t[1] * 1e3f, t[2] * 1e3f);
+        }
+        std::fclose(fp);
+      }
+    }
   }
   return 0;
 }

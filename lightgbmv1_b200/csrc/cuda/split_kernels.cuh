@@ -785,83 +785,99 @@ __device__ void commit_and_select_global(const DevView& V, int lane) {
   if (lane == 0) { c->num_items = ni; c->round += 1; }
 }
 
-// warp 0, training, trees of up to 256 leaves: DECIDE steps 2 and 3 of the control step without touching the leaf
-// table.  Every lane keeps the keys and expanded flags of its 8 leaves (leaf = lane + 32 * slot) in registers, so a
-// pass is 8 local compares and one warp arg-max; the children's keys of every expanded leaf were staged in shared
-// memory (s_ck) by the whole block.  Output: the leaves to commit, in order (s_commit, *s_nc) -- the copies are then
-// done by all warps in parallel -- plus the next round's items and the done flag in DevCtl.
+// Control step, trees of up to 256 leaves.  Leaf keys are handled as integers: `gk` = order-preserving 64-bit image
+// of the gain (larger = better), `tie` = real feature << 16 | leaf (smaller = better; -1 counts as INT_MAX as in
+// SplitInfo::operator>), so "a beats b" is two integer compares.
 #define CTRL_SLOTS 8
 #define CTRL_MAX_LEAVES (32 * CTRL_SLOTS)
-__device__ void plan_commits(const DevView& V, int lane, const SplitKey (*s_ck)[2], int* s_commit, int* s_nc) {
+struct CtrlShared {
+  SplitKey ck[CTRL_MAX_LEAVES][2];          // children's keys of every expanded leaf (staged by the whole block)
+  unsigned long long gk[CTRL_MAX_LEAVES];    // after the commit loop: final key of every open leaf ...
+  unsigned long long tie[CTRL_MAX_LEAVES];
+  int pad[CTRL_MAX_LEAVES];                  // ... its packed split descriptor
+  int eligible[CTRL_MAX_LEAVES];             // ... and whether it may be expanded next (open, not expanded, gain > 0)
+  int ex[CTRL_MAX_LEAVES], pos[CTRL_MAX_LEAVES];  // expanded flag, gain > 0
+  int commit[CTRL_MAX_LEAVES];               // leaves to commit, in order
+  int nc, done, nl;
+};
+__device__ __forceinline__ unsigned long long gain_key64(double g) {
+  unsigned long long u = (unsigned long long)__double_as_longlong(g);
+  return (u >> 63) ? ~u : (u | 0x8000000000000000ull);
+}
+__device__ __forceinline__ unsigned long long tie_key64(int real_feature, int leaf) {
+  return ((unsigned long long)(real_feature == -1 ? 0x7fffffffu : (unsigned)real_feature) << 16) | (unsigned)leaf;
+}
+
+// all threads: thread l loads the key of leaf l into the shared arrays
+__device__ void ctrl_load_keys(const DevView& V, CtrlShared& C, int nl) {
+  const int l = threadIdx.x;  // FS_THREADS == CTRL_MAX_LEAVES
+  C.gk[l] = 0; C.tie[l] = ~0ull; C.pad[l] = 0; C.ex[l] = 0; C.pos[l] = 0;
+  if (l < nl) {
+    const SplitKey key = load_key_cg(&V.leaf_key[l]);
+    C.gk[l] = gain_key64(key.gain); C.tie[l] = tie_key64(key.real_feature, l); C.pad[l] = key.pad; C.pos[l] = key.gain > 0.0;
+    const int ex = __ldcg(&V.expanded[l]);
+    C.ex[l] = ex;
+    if (ex) { C.ck[l][0] = load_key_cg(&V.spec[l].key[0]); C.ck[l][1] = load_key_cg(&V.spec[l].key[1]); }
+  }
+}
+
+// warp 0: step 2 -- which leaves are committed, in the reference's order (ArgMax over best_split_per_leaf_).  The
+// keys live in shared memory (leaf = lane + 32 * slot: conflict-free); a pass is 8 local integer compares and one warp
+// arg-max; a commit overwrites the two entries it changes with the children's keys.
+__device__ void plan_commits(const DevView& V, int lane, CtrlShared& C) {
   DevCtl* c = V.ctl;
   const int max_leaves = V.p.num_leaves;
   int nl = c->num_leaves;
-  SplitKey key[CTRL_SLOTS];
-  int ex[CTRL_SLOTS];
-  unsigned taken = 0;  // bit per slot: chosen as an item of the next round
-#pragma unroll
-  for (int k = 0; k < CTRL_SLOTS; ++k) {
-    const int l = lane + 32 * k;
-    key[k] = none_key(); ex[k] = 0;
-    if (l < nl) { key[k] = load_key_cg(&V.leaf_key[l]); ex[k] = __ldcg(&V.expanded[l]); }
-  }
-  // arg-max over the open leaves; want < 0: all, else only leaves with expanded flag == want that are not taken
-  auto best = [&](int want, SplitKey* out, int* out_ex) -> int {
-    double bg = LGB_MIN_SCORE; int bf = -1, bl = -1, bp = 0, be = 0;
+  int done = 0, nc = 0;
+  while (true) {
+    unsigned long long bg = 0, bt = ~0ull; int bl = -1;
 #pragma unroll
     for (int k = 0; k < CTRL_SLOTS; ++k) {
       const int l = lane + 32 * k;
-      if (l >= nl) continue;
-      if (want >= 0 && (ex[k] != want || ((taken >> k) & 1u))) continue;
-      if (bl < 0 || split_better(key[k].gain, key[k].real_feature, bg, bf)) {
-        bg = key[k].gain; bf = key[k].real_feature; bl = l; bp = key[k].pad; be = ex[k];
+      if (l < nl) {
+        const unsigned long long g = C.gk[l], t = C.tie[l];
+        if (bl < 0 || g > bg || (g == bg && t < bt)) { bg = g; bt = t; bl = l; }
       }
     }
-    const unsigned tie = bf == -1 ? 0x7fffffffu : (unsigned)bf;
-    const int w = warp_argmax(bg, tie, (unsigned)bl, bl >= 0 && bg == bg);  // first leaf with the best (gain, feature)
-    if (w < 0) return -1;
-    out->gain = __shfl_sync(FULL_MASK, bg, w); out->real_feature = __shfl_sync(FULL_MASK, bf, w);
-    out->pad = __shfl_sync(FULL_MASK, bp, w);
-    *out_ex = __shfl_sync(FULL_MASK, be, w);
-    return __shfl_sync(FULL_MASK, bl, w);
-  };
-  int done = 0, nc = 0;
-  SplitKey k; int kex = 0;
-  while (true) {
-    const int bl = best(-1, &k, &kex);
-    if (bl < 0 || !(k.gain > 0.0)) { done = 1; break; }  // "No further splits with positive gain"
-    if (kex == 0) break;                                  // its children are not known yet
-    const SplitKey k0 = s_ck[bl][0], k1 = s_ck[bl][1];
+    const unsigned ghi = (unsigned)(bg >> 32), glo = (unsigned)bg;
+    bool a = bl >= 0;
+    const unsigned m1 = __reduce_max_sync(FULL_MASK, a ? ghi : 0u);
+    a = a && ghi == m1;
+    unsigned bal = __ballot_sync(FULL_MASK, a);
+    if (bal & (bal - 1)) {
+      const unsigned m2 = __reduce_max_sync(FULL_MASK, a ? glo : 0u);
+      a = a && glo == m2;
+      bal = __ballot_sync(FULL_MASK, a);
+      if (bal & (bal - 1)) {
+        const unsigned m3 = __reduce_min_sync(FULL_MASK, a ? (unsigned)(bt >> 32) : 0xffffffffu);
+        a = a && (unsigned)(bt >> 32) == m3;
+        const unsigned m4 = __reduce_min_sync(FULL_MASK, a ? (unsigned)bt : 0xffffffffu);
+        a = a && (unsigned)bt == m4;
+        bal = __ballot_sync(FULL_MASK, a);
+      }
+    }
+    if (bal == 0) { done = 1; break; }
+    bl = __shfl_sync(FULL_MASK, bl, __ffs(bal) - 1);
+    if (!C.pos[bl]) { done = 1; break; }   // "No further splits with positive gain"
+    if (!C.ex[bl]) break;                  // its children are not known yet
     const int R = nl;
-    if (lane == 0) s_commit[nc] = bl;
+    if (lane == 0) {
+      C.commit[nc] = bl;
+      const SplitKey k0 = C.ck[bl][0], k1 = C.ck[bl][1];
+      C.gk[bl] = gain_key64(k0.gain); C.tie[bl] = tie_key64(k0.real_feature, bl); C.pad[bl] = k0.pad; C.pos[bl] = k0.gain > 0.0; C.ex[bl] = 0;
+      C.gk[R] = gain_key64(k1.gain); C.tie[R] = tie_key64(k1.real_feature, R); C.pad[R] = k1.pad; C.pos[R] = k1.gain > 0.0; C.ex[R] = 0;
+    }
+    __syncwarp();
     ++nc;
-#pragma unroll
-    for (int s = 0; s < CTRL_SLOTS; ++s) {
-      if (lane + 32 * s == bl) { key[s] = k0; ex[s] = 0; }
-      if (lane + 32 * s == R) { key[s] = k1; ex[s] = 0; }
-    }
     nl += 1;
-    if (nl >= max_leaves) { done = 2; break; }            // the tree is full
+    if (nl >= max_leaves) { done = 2; break; }  // the tree is full
   }
-  int ni = 0;
-  if (!done) {
-    int K = c->lookahead;
-    if (K > max_leaves - nl) K = max_leaves - nl;
-    for (int e = 0; e < K; ++e) {
-      const int bl = best(0, &k, &kex);
-      if (bl < 0 || !(k.gain > 0.0)) break;
 #pragma unroll
-      for (int s = 0; s < CTRL_SLOTS; ++s) if (lane + 32 * s == bl) taken |= 1u << s;
-      if (lane == 0) {
-        c->item_leaf[ni] = bl;
-        c->item_feature[ni] = k.pad & ((1 << KEY_FEAT_BITS) - 1);
-        c->item_threshold[ni] = (k.pad >> KEY_FEAT_BITS) & 511;
-        c->item_default_left[ni] = (k.pad >> (KEY_FEAT_BITS + 9)) & 1;
-      }
-      ++ni;
-    }
+  for (int k = 0; k < CTRL_SLOTS; ++k) {
+    const int l = lane + 32 * k;
+    C.eligible[l] = (l < nl && !done && C.pos[l] && C.ex[l] == 0) ? 1 : 0;
   }
-  if (lane == 0) { c->num_items = ni; c->round += 1; if (done) c->done = done; *s_nc = nc; }
+  if (lane == 0) { C.nc = nc; C.done = done; C.nl = nl; }
 }
 
 // mode 0: training.  grid = (num_features, 2 * LGB_KMAX): blockIdx.y = 2 * item + sel; sel 0 scans the smaller child of
@@ -913,12 +929,14 @@ __global__ void __launch_bounds__(FS_THREADS, 4) k_find_split(DevView V, int mod
   if (!s_last) return;
   // ---- control step, last block only.  Step 1: every warp reduces feat_key rows (one leaf each) and stores that
   // leaf's best split where it belongs.
-  __shared__ SplitKey s_ck[CTRL_MAX_LEAVES][2];
-  __shared__ int s_commit[CTRL_MAX_LEAVES];
-  __shared__ int s_nc;
+  __shared__ CtrlShared C;
   const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
 #ifdef LGBCU_STAGE_TIMERS
   long long tc0 = clock64();
+  long long tq_ = tc0;
+#define QSTAGE(i) do { if (threadIdx.x == 0) { long long t_ = clock64(); g_stage_cycles[16 + (i)] += (unsigned long long)(t_ - tq_); tq_ = t_; } } while (0)
+#else
+#define QSTAGE(i) do {} while (0)
 #endif
   if (threadIdx.x == 0) c->feat_done = 0;
   if (mode == 1 || root_round) {
@@ -943,6 +961,7 @@ __global__ void __launch_bounds__(FS_THREADS, 4) k_find_split(DevView V, int mod
   }
   __threadfence_block();
   __syncthreads();
+  QSTAGE(0);
   if (mode == 1) return;
   if (!root_round && threadIdx.x < ni) V.expanded[c->item_leaf[threadIdx.x]] = 1;
   __threadfence_block();
@@ -952,15 +971,47 @@ __global__ void __launch_bounds__(FS_THREADS, 4) k_find_split(DevView V, int mod
     if (warp == 0) commit_and_select_global(V, lane);
     return;
   }
-  // steps 2 and 3: stage the children's keys of every expanded leaf, let warp 0 decide, then all warps copy
-  for (int l = threadIdx.x; l < nl0; l += FS_THREADS) {
-    if (__ldcg(&V.expanded[l])) { s_ck[l][0] = load_key_cg(&V.spec[l].key[0]); s_ck[l][1] = load_key_cg(&V.spec[l].key[1]); }
+  // step 2: stage every open leaf's key (and the children's keys of the expanded ones), let warp 0 decide the commits
+  ctrl_load_keys(V, C, nl0);
+  __syncthreads();
+  QSTAGE(1);
+  if (warp == 0) plan_commits(V, lane, C);
+  __syncthreads();
+  QSTAGE(2);
+  // step 3, all threads: the next round's items = the K eligible leaves with the best keys; a leaf's item index is the
+  // number of eligible leaves that beat it
+  {
+    int K = c->lookahead;
+    if (K > V.p.num_leaves - C.nl) K = V.p.num_leaves - C.nl;
+    const int l = threadIdx.x;  // FS_THREADS == CTRL_MAX_LEAVES
+    const int mine = C.eligible[l];
+    int rank = 0;
+    if (mine) {
+      const unsigned long long g = C.gk[l], t = C.tie[l];
+      const int nlf = C.nl;
+      for (int m = 0; m < nlf; ++m) {
+        const unsigned long long gm = C.gk[m], tm = C.tie[m];
+        rank += (C.eligible[m] && (gm > g || (gm == g && tm < t))) ? 1 : 0;
+      }
+      if (rank < K) {
+        const int pd = C.pad[l];
+        c->item_leaf[rank] = l;
+        c->item_feature[rank] = pd & ((1 << KEY_FEAT_BITS) - 1);
+        c->item_threshold[rank] = (pd >> KEY_FEAT_BITS) & 511;
+        c->item_default_left[rank] = (pd >> (KEY_FEAT_BITS + 9)) & 1;
+      }
+    }
+    const int n_elig = __syncthreads_count(mine);
+    if (threadIdx.x == 0) {
+      c->num_items = n_elig < K ? n_elig : (K > 0 ? K : 0);
+      c->round += 1;
+      if (C.done) c->done = C.done;
+    }
   }
-  __syncthreads();
-  if (warp == 0) plan_commits(V, lane, s_ck, s_commit, &s_nc);
-  __syncthreads();
-  const int nc = s_nc;
-  for (int i = warp; i < nc; i += FS_WARPS) commit_leaf_as(V, s_commit[i], nl0 + i, ns0 + i, lane);
+  QSTAGE(3);
+  const int nc = C.nc;
+  for (int i = warp; i < nc; i += FS_WARPS) commit_leaf_as(V, C.commit[i], nl0 + i, ns0 + i, lane);
+  QSTAGE(4);
   if (threadIdx.x == 0) { c->num_leaves = nl0 + nc; c->num_splits = ns0 + nc; }
 #ifdef LGBCU_STAGE_TIMERS
   if (threadIdx.x == 0) { g_stage_cycles[6] += (unsigned long long)(clock64() - tc0); g_stage_cycles[7] += 1; }

@@ -17,3 +17,14 @@ for _ in range(3):
     ours.check(lib.LGBM_B200_BoosterPhases(b, ph))
     print("K=%s phases ms: hist %.2f find+control %.2f partition %.2f; rounds enqueued %d used %d" % (
         os.environ.get("LGBCU_LOOKAHEAD", "default"), ph[0], ph[2], ph[4], ph[6], ph[7]))
+if hasattr(lib, "lgbcu_debug_stages"):   # debug build (tools/build_dbg.sh): block-0 stage times
+    out = (C.c_ulonglong * 32)()
+    lib.lgbcu_debug_stages(out, 1)
+    ours.update(b)
+    lib.lgbcu_debug_stages(out, 0)
+    ours.check(lib.LGBM_B200_BoosterPhases(b, ph))
+    r = max(1.0, ph[7])
+    us = lambda i: round(out[i] / 1.965e3 / r, 2)
+    print("per round, block 0 (us): find [ctl, load+fix, -, chains+scans, gains, ticket, control]:", [us(i) for i in range(7)],
+          " partition [ctl+leaf, flags, barrier, prefix, scatter]:", [us(8 + i) for i in range(5)],
+          " control [reduce+store, stage keys, plan, select, copies]:", [us(16 + i) for i in range(5)])
