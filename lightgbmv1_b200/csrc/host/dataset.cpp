@@ -248,6 +248,7 @@ void Dataset::BinAllRows(const void* data, int data_type, int32_t nrow, int32_t 
 }
 
 Dataset::~Dataset() {
+  if (label_pinned_) lgbcu_unpin_host_buffer(meta_.label.data());
   if (bins_pinned_) lgbcu_unpin_host_buffer(bins_.data());
 }
 
@@ -271,7 +272,10 @@ void Dataset::SetFloatField(const char* name, const float* data, int n) {
   const std::string k(name);
   if (k == "label" || k == "target") {
     if (n != num_data_) Log::Fatal("Length of label is not same with #data");
+    if (label_pinned_) { lgbcu_unpin_host_buffer(meta_.label.data()); label_pinned_ = false; }
     meta_.label.assign(data, data + n);
+    // uploaded at every LGBM_BoosterCreate: page-lock it like the bin matrix (a no-op without a device)
+    label_pinned_ = lgbcu_pin_host_buffer(meta_.label.data(), meta_.label.size() * sizeof(label_t)) == 0;
   } else if (k == "weight" || k == "weights") {
     if (data == nullptr || n == 0) { meta_.weights.clear(); return; }
     if (n != num_data_) Log::Fatal("Length of weights is not same with #data");

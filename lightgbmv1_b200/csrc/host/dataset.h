@@ -62,6 +62,7 @@ class Dataset {
   std::vector<int> inner_to_real_, real_to_inner_;
   std::vector<uint8_t> bins_;
   bool bins_pinned_ = false;  // page-locked for the upload (lgbcu_pin_host_buffer)
+  bool label_pinned_ = false;
   std::vector<std::string> feature_names_;
   Metadata meta_;
 };

@@ -28,3 +28,11 @@ if hasattr(lib, "lgbcu_debug_stages"):   # debug build (tools/build_dbg.sh): blo
     print("per round, block 0 (us): find [ctl, load+fix, -, chains+scans, gains, ticket, control]:", [us(i) for i in range(7)],
           " partition [ctl+leaf, flags, barrier, prefix, scatter]:", [us(8 + i) for i in range(5)],
           " control [reduce+store, stage keys, plan, select, copies]:", [us(16 + i) for i in range(5)])
+if hasattr(lib, "lgbcu_debug_hist_stages"):
+    o8 = (C.c_ulonglong * 8)()
+    lib.lgbcu_debug_hist_stages(o8, 1)
+    ours.update(b)
+    lib.lgbcu_debug_hist_stages(o8, 0)
+    ours.check(lib.LGBM_B200_BoosterPhases(b, ph))
+    r = max(1.0, ph[7])
+    print("hist block 0 per round (us) [load+zero, accumulate, sync1, reduce+red, sync2]:", [round(o8[i] / 1.965e3 / r, 2) for i in range(5)])
