@@ -34,6 +34,10 @@ import time
 
 import numpy as np
 
+# rank 0 must print ONE JSON line on stdout: keep NCCL's version banner (NCCL_DEBUG=VERSION) out of it
+if os.environ.get("NCCL_DEBUG", "").upper() == "VERSION":
+    os.environ["NCCL_DEBUG"] = "WARN"
+
 ROOT = os.path.dirname(os.path.abspath(__file__))
 sys.path.insert(0, ROOT)
 sys.path.insert(0, os.path.join(ROOT, "tests"))
@@ -261,6 +265,10 @@ def run_ours(args):
         pass
     achieved = (hist_bytes.value / 1e9) / (hist_ms.value / 1e3) if hist_ms.value > 0 else 0.0
 
+    if use_dist:
+        ours.booster_free(b)
+        dist.barrier()
+        dist.destroy_process_group()
     if rank != 0:
         return 0
     # ---- cpu_baseline (N=1 only): the reference CPU learner on the same workload, few iterations
