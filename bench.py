@@ -34,9 +34,15 @@ import time
 
 import numpy as np
 
-# rank 0 must print ONE JSON line on stdout: keep NCCL's version banner (NCCL_DEBUG=VERSION) out of it
-if os.environ.get("NCCL_DEBUG", "").upper() == "VERSION":
-    os.environ["NCCL_DEBUG"] = "WARN"
+# rank 0 must print ONE JSON line on stdout.  Libraries (NCCL's version banner, LightGBM's log) write to fd 1 as well,
+# so everything but that line is sent to stderr: fd 1 is pointed at fd 2 and the line goes to the saved descriptor.
+_REAL_STDOUT = os.dup(1)
+os.dup2(2, 1)
+
+
+def emit(line):
+    os.write(_REAL_STDOUT, (json.dumps(line) + "\n").encode())
+
 
 ROOT = os.path.dirname(os.path.abspath(__file__))
 sys.path.insert(0, ROOT)
@@ -119,7 +125,7 @@ def run_reference(args):
         return 0
     import capi
     if not os.path.exists(capi.REF_SO):
-        print(json.dumps({"impl": "reference", "unavailable": "oracle/_ref/lib_lightgbm.so not built (make -C oracle ref)"}))
+        emit({"impl": "reference", "unavailable": "oracle/_ref/lib_lightgbm.so not built (make -C oracle ref)"})
         return 0
     cores = os.cpu_count() or 1
     n = args.rows
@@ -146,7 +152,7 @@ def run_reference(args):
                          "sample": f"full workload, {args.steps} iterations after {args.warmup} warm-up, force_col_wise"},
         "e2e": {"value": v, "unit": "iters/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
     }
-    print(json.dumps(line))
+    emit(line)
     return 0
 
 
@@ -313,7 +319,7 @@ def run_ours(args):
         "cpu_baseline": cpu,
         "train_check": {"mean_score": float(np.mean(scores))},
     }
-    print(json.dumps(line))
+    emit(line)
     return 0
 
 
