@@ -718,9 +718,9 @@ int lgbcu_add_score_by_partition(LgbCuContext* c, const double* leaf_value, int3
   CU(cudaSetDevice(c->device));
   CU(cudaMemcpyAsync(c->d_leaf_value, leaf_value, sizeof(double) * num_leaves, cudaMemcpyHostToDevice, c->stream));
   const DevView V = c->view();
-  int gx = grid_for(c, (c->root_count + num_leaves - 1) / num_leaves, 256, 4);
-  if (gx > 64) gx = 64;
-  LAUNCH(k_add_score_partition, dim3(gx, num_leaves), 256, 0, c->stream, V, c->d_leaf_value, c->d_score);
+  // one block per 4096-position chunk; a leaf's last chunk may be partial, hence the num_leaves spare blocks
+  const int chunks = (c->root_count + ADD_SCORE_CHUNK - 1) / ADD_SCORE_CHUNK + num_leaves;
+  LAUNCH(k_add_score_partition, chunks, ADD_SCORE_THREADS, 0, c->stream, V, num_leaves, c->d_leaf_value, c->d_score);
   CU(cudaGetLastError());
   // leaf_value is pageable host memory: the async copy above has been staged by the time it returns
   return 0;

@@ -163,14 +163,55 @@ __global__ void k_hist_subtract(DevView V, int parent_leaf, int smaller_leaf) {
 }
 
 // SerialTreeLearner::AddPredictionToScore (src/treelearner/serial_tree_learner.h:96-111):
-// score[idx] += leaf_value[leaf] for every row of every leaf range.  grid = (blocks, num_leaves)
-__global__ void k_add_score_partition(DevView V, const double* __restrict__ leaf_value, double* __restrict__ score) {
-  const int leaf = blockIdx.y;
-  const DevLeaf L = V.leaves[leaf];
-  const double v = leaf_value[leaf];
-  const int* idx = V.indices[L.buf] + L.begin;
-  for (int i = blockIdx.x * blockDim.x + threadIdx.x; i < L.count; i += gridDim.x * blockDim.x) {
-    score[idx[i]] += v;
+// score[idx] += leaf_value[leaf] for every row of every leaf range.  Leaves differ in size by orders of magnitude, so
+// the work is cut into chunks of ADD_SCORE_CHUNK positions: every block derives the chunk -> (leaf, offset) map from
+// the leaf table (a 1024-entry block scan), then handles the chunk with its own index.
+#define ADD_SCORE_CHUNK 4096
+#define ADD_SCORE_THREADS 256
+__global__ void __launch_bounds__(ADD_SCORE_THREADS) k_add_score_partition(DevView V, int num_leaves,
+                                                                           const double* __restrict__ leaf_value,
+                                                                           double* __restrict__ score) {
+  __shared__ int s_first[1025];  // first chunk of leaf l (exclusive prefix of the chunk counts)
+  __shared__ int s_warp[ADD_SCORE_THREADS / 32];
+  __shared__ int s_carry;
+  const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+  int target = blockIdx.x;
+  for (int base = 0; base < num_leaves; base += 1024) {  // trees of more than 1024 leaves: window by window
+    if (tid == 0) s_carry = 0;
+    __syncthreads();
+    const int nwin = min(1024, num_leaves - base);
+    for (int off = 0; off < nwin; off += ADD_SCORE_THREADS) {
+      const int l = off + tid;
+      const int v = l < nwin ? (V.leaves[base + l].count + ADD_SCORE_CHUNK - 1) / ADD_SCORE_CHUNK : 0;
+      int inc = v;
+      for (int o = 1; o < 32; o <<= 1) { const int x = __shfl_up_sync(0xffffffffu, inc, o); if (lane >= o) inc += x; }
+      if (lane == 31) s_warp[warp] = inc;
+      __syncthreads();
+      int woff = 0;
+      for (int w = 0; w < warp; ++w) woff += s_warp[w];
+      const int excl = s_carry + woff + inc - v;
+      if (l < nwin) s_first[l] = excl;
+      __syncthreads();
+      if (tid == ADD_SCORE_THREADS - 1) s_carry = excl + v;
+      __syncthreads();
+    }
+    const int total = s_carry;
+    if (tid == 0) s_first[nwin] = total;
+    __syncthreads();
+    if (target < total) {
+      int lo = 0, hi = nwin - 1;  // last leaf whose first chunk is <= target (it cannot be an empty one)
+      while (lo < hi) { const int mid = (lo + hi + 1) >> 1; if (s_first[mid] <= target) lo = mid; else hi = mid - 1; }
+      const int leaf = base + lo;
+      const DevLeaf L = V.leaves[leaf];
+      const double v = leaf_value[leaf];
+      const int* idx = V.indices[L.buf] + L.begin;
+      const int c0 = (target - s_first[lo]) * ADD_SCORE_CHUNK;
+      const int c1 = min(L.count, c0 + ADD_SCORE_CHUNK);
+      for (int i = c0 + tid; i < c1; i += ADD_SCORE_THREADS) score[idx[i]] += v;
+      return;
+    }
+    target -= total;
+    __syncthreads();
   }
 }
 
