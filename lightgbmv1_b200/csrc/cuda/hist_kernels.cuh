@@ -10,30 +10,34 @@
 //   global atomics : one thread per (row, 16-feature chunk), REDG.ADD.64 straight into the pool slot.  Tiny
 //                    leaves (< HIST_SMALL_LEAF_ROWS rows), where zeroing / flushing a 64 KB sub-histogram would
 //                    cost more than the rows themselves.
-//   block shared   : a block owns ONE 64 KB shared-memory sub-histogram for a tile of 16 features x {g,h} and a
-//                    slice of the leaf's rows; all 16 warps of the block accumulate into it.  Lane l of every warp
-//                    = column (channel, feature), so the 32 lanes of an instruction always hit 32 different
-//                    columns, and with the layout [bin][32 columns] of 32-bit words lane l always sits on bank l:
-//                    no bank conflicts for any bin pattern.  sm_100 has native shared-memory atomics only for
-//                    32-bit integers, so a 64-bit entry is kept as two words: ATOMS.ADD on the low word returns the
-//                    old value, the carry (old + v wrapped) is added together with the high word by a second
-//                    ATOMS.ADD.  Each wrap is seen by exactly the add that caused it and addition commutes, so the
-//                    pair (hi, lo) read after the block barrier is the exact 64-bit sum whatever the interleaving.
-//                    Measured (tools/ubench/atoms.cu): 3.3 cycles per (row, tile) per SM with 32 resident warps
-//                    against 12.3 for the former warp-private LDS/IADD/STS design (3 warps fit).  The
-//                    sub-histogram is flushed once per block with REDG.ADD.64 (zero entries skipped).
+//   block shared   : a block (32 warps, one per SM) owns one 64 KB shared-memory sub-histogram per tile of 16 features
+//                    x {g,h} -- two tiles at once, so that one 32-byte row read, one (g,h) read and one staging pass
+//                    serve 32 features -- and a slice of the leaf's rows.  Lane l of every warp = column (channel,
+//                    feature), so the 32 lanes of an instruction always hit 32 different columns, and with the
+//                    layout [bin][32 columns] of 32-bit words lane l always sits on bank l: no bank conflicts for
+//                    any bin pattern.  sm_100 has native shared-memory atomics only for 32-bit integers, so a 64-bit
+//                    entry is kept as two words: ATOMS.ADD on the low word returns the old value, the carry
+//                    (old + v wrapped) is added together with the high word by a second ATOMS.ADD.  Each wrap is seen
+//                    by exactly the add that caused it and addition commutes, so the pair (hi, lo) read after the
+//                    block barrier is the exact 64-bit sum whatever the interleaving.  Measured in isolation
+//                    (tools/ubench/atoms.cu): 3.3 cycles per (row, tile) per SM with 32 resident warps against 12.3
+//                    for the round's first design (a private LDS/IADD/STS sub-histogram per warp; 3 warps fit).
+//                    The blocks of a cluster (2) work on row slices of the same tile pair, sum their sub-histograms
+//                    through distributed shared memory and flush once with REDG.ADD.64 (zero entries skipped).
 #pragma once
 #include <cooperative_groups.h>
 #include "dev_types.cuh"
 
-#define HIST_CLUSTER 4                            /* blocks per thread-block cluster: they reduce their sub-histograms through DSMEM */
-#define HIST_THREADS 512                          /* block size of the histogram kernel: 16 warps */
+#define HIST_CLUSTER 2                            /* blocks per thread-block cluster: they reduce their sub-histograms through DSMEM
+                                                     (2 x 1024 threads x 176 KB: 74 clusters = all 148 SMs; 4 leaves 16 SMs idle) */
+#define HIST_THREADS 1024                         /* block size of the histogram kernel: 32 warps */
 #define HIST_WARPS (HIST_THREADS / 32)
-#define HIST_BLOCKS_PER_SM 2                      /* 2 x 80 KB of shared memory, 32 resident warps per SM */
+#define HIST_BLOCKS_PER_SM 1                      /* 176 KB of shared memory */
+#define HIST_TILES 2                              /* 16-feature tiles a block accumulates at once */
 #define HIST_ROWS_SMEM 256                        /* bin rows of the sub-histogram */
 #define HIST_SUB_BYTES (HIST_ROWS_SMEM * 32 * 8)  /* 64 KB: lo words [256][32], then hi words [256][32] */
-#define HIST_STAGE_BYTES 1024                     /* per warp: 32 x 16 B bins + 2 x 32 x 8 B (gq | hq) */
-#define HIST_SMEM_BYTES (HIST_SUB_BYTES + HIST_WARPS * HIST_STAGE_BYTES)
+#define HIST_STAGE_BYTES 1536                     /* per warp: 32 x 32 B bins (two tiles, interleaved) + 2 x 32 x 8 B (gq | hq) */
+#define HIST_SMEM_BYTES (HIST_TILES * HIST_SUB_BYTES + HIST_WARPS * HIST_STAGE_BYTES)
 #define HIST_SMALL_LEAF_ROWS 256
 #define HIST_MIN_ROWS_PER_WARP 16                 /* rows a warp should at least get before another block is recruited */
 
@@ -87,47 +91,42 @@ __device__ void hist_shared_path(const DevView& V, const DevLeaf& L, bool identi
   const double sg = c->scale_g, sh = c->scale_h;
   const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
   const int fl = lane & 15, ch = lane >> 4;
-  unsigned* lo = reinterpret_cast<unsigned*>(smem);
-  unsigned* hi = lo + HIST_ROWS_SMEM * 32;
-  unsigned* lo_l = lo + lane;  // this lane's column
-  unsigned char* stage = smem + HIST_SUB_BYTES + warp * HIST_STAGE_BYTES;
-  uint4* sbins = reinterpret_cast<uint4*>(stage);      // [32] one 16-byte chunk per staged row
-  i64* svals = reinterpret_cast<i64*>(stage + 512);    // [2][32]: gq of the 32 staged rows, then hq
-  const unsigned char* sb8 = stage + fl;
-  const longlong2* sv2 = reinterpret_cast<const longlong2*>(stage + 512 + ch * 256);
+  unsigned* lo = reinterpret_cast<unsigned*>(smem);   // tile A: lo [256][32], hi [256][32]; tile B follows
+  unsigned* lo_l = lo + lane;                          // this lane's column
+  unsigned char* stage = smem + HIST_TILES * HIST_SUB_BYTES + warp * HIST_STAGE_BYTES;
+  uint4* sbins = reinterpret_cast<uint4*>(stage);      // [32 rows][32 B]: byte 2f = tile A feature f, 2f+1 = tile B
+  i64* svals = reinterpret_cast<i64*>(stage + 1024);   // [2][32]: gq of the 32 staged rows, then hq
+  const unsigned short* sb16 = reinterpret_cast<const unsigned short*>(stage) + fl;
+  const longlong2* sv2 = reinterpret_cast<const longlong2*>(stage + 1024 + ch * 256);
 
   const int NT = V.num_tiles16;
-  // Work units: (tile, group of HIST_CLUSTER row slices), dealt round-robin to the clusters; the blocks of a cluster
-  // take the HIST_CLUSTER slices of one unit, so that their sub-histograms cover the same tile and can be summed
-  // through distributed shared memory before anything goes to global memory.
+  const int NP = (NT + HIST_TILES - 1) / HIST_TILES;   // tile pairs
+  // Work units: (tile pair, group of HIST_CLUSTER row slices).  A block accumulates BOTH 16-feature tiles of a pair:
+  // one 32-byte row read, one (g,h) read and one staging pass serve 32 features.
   namespace cg = cooperative_groups;
   cg::cluster_group cluster = cg::this_cluster();
   const int rank = (int)cluster.block_rank();
   const int nclusters = nblocks / HIST_CLUSTER, cluster_id = bid / HIST_CLUSTER;
   int PG = (L.count + HIST_CLUSTER * HIST_WARPS * min_rows - 1) / (HIST_CLUSTER * HIST_WARPS * min_rows);
-  int cap = nclusters / NT; if (cap < 1) cap = 1;
+  int cap = nclusters / NP; if (cap < 1) cap = 1;
   if (PG > cap) PG = cap;
   if (PG < 1) PG = 1;
   int per_block = (L.count + PG * HIST_CLUSTER - 1) / (PG * HIST_CLUSTER);
   per_block = (per_block + 31) / 32 * 32;
-
   const int* idx = V.indices[L.buf] + L.begin;
   HistEntry* out = V.pool + (size_t)L.slot * V.total_bin;
-
 #ifdef LGBCU_STAGE_TIMERS
   long long ht_ = clock64();
 #endif
-  for (int unit = cluster_id; unit < NT * PG; unit += nclusters) {
-    // tile is the fast index: neighbouring clusters work on the same row slice at the same time, so the second
-    // tile's read of a row (same 32-byte sector) is served by L2 instead of going to DRAM again
-    const int group = unit / NT, tile = unit - group * NT, part = group * HIST_CLUSTER + rank;
+  for (int unit = cluster_id; unit < NP * PG; unit += nclusters) {
+    const int group = unit / NP, pair = unit - group * NP, part = group * HIST_CLUSTER + rank;
+    const int tile0 = pair * HIST_TILES;
+    const bool two = tile0 + 1 < NT;   // the last pair of an odd tile count has one tile only
     int b0 = part * per_block; if (b0 > L.count) b0 = L.count;
     int b1 = b0 + per_block; if (b1 > L.count) b1 = L.count;
-    const uint8_t* colbase = V.bins + tile * 16;
-    // software pipeline, two deep: while batch k is accumulated the row data of batch k+1 and the row index of
-    // batch k+2 are in flight; the first loads are issued before the sub-histogram is zeroed
+    const uint8_t* colbase = V.bins + tile0 * 16;
     const int step = HIST_WARPS * 32;
-    uint4 nq = make_uint4(0, 0, 0, 0);
+    uint4 nqa = make_uint4(0, 0, 0, 0), nqb = make_uint4(0, 0, 0, 0);
     float ng = 0.f, nh = 0.f;
     int prow = -1;
     int base = b0 + warp * 32;
@@ -135,7 +134,9 @@ __device__ void hist_shared_path(const DevView& V, const DevLeaf& L, bool identi
       const int pos = base + lane;
       if (pos < b1) {
         const int row = identity ? pos : idx[pos];
-        nq = *reinterpret_cast<const uint4*>(colbase + (size_t)row * V.row_stride);
+        const uint4* rp = reinterpret_cast<const uint4*>(colbase + (size_t)row * V.row_stride);
+        nqa = rp[0];
+        if (two) nqb = rp[1];
         { const float2 gh = V.gh[row]; ng = gh.x; nh = gh.y; }
       }
       const int pos1 = pos + step;
@@ -145,17 +146,27 @@ __device__ void hist_shared_path(const DevView& V, const DevLeaf& L, bool identi
       uint4* z = reinterpret_cast<uint4*>(smem);
       const uint4 zero = make_uint4(0, 0, 0, 0);
 #pragma unroll
-      for (int i = tid; i < HIST_SUB_BYTES / 16; i += HIST_THREADS) z[i] = zero;
+      for (int i = tid; i < HIST_TILES * HIST_SUB_BYTES / 16; i += HIST_THREADS) z[i] = zero;
     }
     __syncthreads();
     HSTAGE(0);
     for (; base < b1; base += step) {
-      sbins[lane] = nq;
+      {
+        // byte-interleave the two tiles of this lane's row: (a0 b0 a1 b1) (a2 b2 a3 b3) per pair of words
+        uint4 w0, w1;
+        w0.x = __byte_perm(nqa.x, nqb.x, 0x5140); w0.y = __byte_perm(nqa.x, nqb.x, 0x7362);
+        w0.z = __byte_perm(nqa.y, nqb.y, 0x5140); w0.w = __byte_perm(nqa.y, nqb.y, 0x7362);
+        w1.x = __byte_perm(nqa.z, nqb.z, 0x5140); w1.y = __byte_perm(nqa.z, nqb.z, 0x7362);
+        w1.z = __byte_perm(nqa.w, nqb.w, 0x5140); w1.w = __byte_perm(nqa.w, nqb.w, 0x7362);
+        sbins[2 * lane] = w0; sbins[2 * lane + 1] = w1;
+      }
       svals[lane] = to_fixed(ng, sg);
       svals[32 + lane] = to_fixed(nh, sh);
-      nq = make_uint4(0, 0, 0, 0); ng = 0.f; nh = 0.f;
+      nqa = make_uint4(0, 0, 0, 0); nqb = make_uint4(0, 0, 0, 0); ng = 0.f; nh = 0.f;
       if (prow >= 0) {
-        nq = *reinterpret_cast<const uint4*>(colbase + (size_t)prow * V.row_stride);
+        const uint4* rp = reinterpret_cast<const uint4*>(colbase + (size_t)prow * V.row_stride);
+        nqa = rp[0];
+        if (two) nqb = rp[1];
         { const float2 gh = V.gh[prow]; ng = gh.x; nh = gh.y; }
       }
       {
@@ -165,10 +176,28 @@ __device__ void hist_shared_path(const DevView& V, const DevLeaf& L, bool identi
       }
       __syncwarp();
       int n = b1 - base; if (n > 32) n = 32;
-      if (n == 32) {
+      if (n == 32 && two) {
 #pragma unroll 8
         for (int j = 0; j < 32; j += 2) {
-          const unsigned c0 = sb8[j * 16], c1 = sb8[(j + 1) * 16];
+          const unsigned c0 = sb16[j * 16], c1 = sb16[(j + 1) * 16];   // (tile A bin) | (tile B bin) << 8
+          const longlong2 v = sv2[j >> 1];
+          const unsigned v0l = (unsigned)v.x, v0h = (unsigned)((unsigned long long)v.x >> 32);
+          const unsigned v1l = (unsigned)v.y, v1h = (unsigned)((unsigned long long)v.y >> 32);
+          unsigned* p0a = lo_l + (c0 & 0xffu) * 32; unsigned* p0b = lo_l + HIST_SUB_BYTES / 4 + (c0 >> 8) * 32;
+          unsigned* p1a = lo_l + (c1 & 0xffu) * 32; unsigned* p1b = lo_l + HIST_SUB_BYTES / 4 + (c1 >> 8) * 32;
+          const unsigned o0a = atomicAdd(p0a, v0l);
+          const unsigned o0b = atomicAdd(p0b, v0l);
+          const unsigned o1a = atomicAdd(p1a, v1l);
+          const unsigned o1b = atomicAdd(p1b, v1l);
+          atomicAdd(p0a + HIST_ROWS_SMEM * 32, v0h + ((o0a + v0l) < o0a ? 1u : 0u));
+          atomicAdd(p0b + HIST_ROWS_SMEM * 32, v0h + ((o0b + v0l) < o0b ? 1u : 0u));
+          atomicAdd(p1a + HIST_ROWS_SMEM * 32, v1h + ((o1a + v1l) < o1a ? 1u : 0u));
+          atomicAdd(p1b + HIST_ROWS_SMEM * 32, v1h + ((o1b + v1l) < o1b ? 1u : 0u));
+        }
+      } else if (n == 32) {  // single tile (F <= 16, or the last pair of an odd tile count)
+#pragma unroll 8
+        for (int j = 0; j < 32; j += 2) {
+          const unsigned c0 = sb16[j * 16] & 0xffu, c1 = sb16[(j + 1) * 16] & 0xffu;
           const longlong2 v = sv2[j >> 1];
           const unsigned v0l = (unsigned)v.x, v0h = (unsigned)((unsigned long long)v.x >> 32);
           const unsigned v1l = (unsigned)v.y, v1h = (unsigned)((unsigned long long)v.y >> 32);
@@ -179,14 +208,19 @@ __device__ void hist_shared_path(const DevView& V, const DevLeaf& L, bool identi
           atomicAdd(p1 + HIST_ROWS_SMEM * 32, v1h + ((o1 + v1l) < o1 ? 1u : 0u));
         }
       } else {
-        const i64* sv = reinterpret_cast<const i64*>(stage + 512 + ch * 256);
+        const i64* sv = reinterpret_cast<const i64*>(stage + 1024 + ch * 256);
         for (int j = 0; j < n; ++j) {
-          const unsigned b = sb8[j * 16];
+          const unsigned cc = sb16[j * 16];
           const i64 v = sv[j];
           const unsigned vl = (unsigned)v, vh = (unsigned)((unsigned long long)v >> 32);
-          unsigned* p = lo_l + b * 32;
-          const unsigned o = atomicAdd(p, vl);
-          atomicAdd(p + HIST_ROWS_SMEM * 32, vh + ((o + vl) < o ? 1u : 0u));
+          unsigned* pa = lo_l + (cc & 0xffu) * 32;
+          const unsigned oa = atomicAdd(pa, vl);
+          atomicAdd(pa + HIST_ROWS_SMEM * 32, vh + ((oa + vl) < oa ? 1u : 0u));
+          if (two) {
+            unsigned* pb = lo_l + HIST_SUB_BYTES / 4 + (cc >> 8) * 32;
+            const unsigned ob = atomicAdd(pb, vl);
+            atomicAdd(pb + HIST_ROWS_SMEM * 32, vh + ((ob + vl) < ob ? 1u : 0u));
+          }
         }
       }
       __syncwarp();
@@ -198,27 +232,29 @@ __device__ void hist_shared_path(const DevView& V, const DevLeaf& L, bool identi
     cluster.sync();
     HSTAGE(2);
     {
-      const int f = tile * 16 + fl;
-      int nslots = 0; i64* dst = nullptr;
-      if (f < V.num_features) {
-        const DevFeat F = V.feats[f];
-        nslots = F.nslots;
-        dst = reinterpret_cast<i64*>(out + F.hist_base) + ch;
-      }
       const unsigned* rlo[HIST_CLUSTER];
 #pragma unroll
       for (int k = 0; k < HIST_CLUSTER; ++k) rlo[k] = cluster.map_shared_rank(lo, k);
+      for (int t = 0; t < (two ? 2 : 1); ++t) {
+        const int f = (tile0 + t) * 16 + fl;
+        int nslots = 0; i64* dst = nullptr;
+        if (f < V.num_features) {
+          const DevFeat F = V.feats[f];
+          nslots = F.nslots;
+          dst = reinterpret_cast<i64*>(out + F.hist_base) + ch;
+        }
+        for (int e0 = rank * (HIST_ROWS_SMEM / HIST_CLUSTER) * 32; e0 < (rank + 1) * (HIST_ROWS_SMEM / HIST_CLUSTER) * 32; e0 += HIST_THREADS) {
+          const int e = e0 + tid;  // column = tid & 31
+          const int b = e >> 5;
+          const int eo = t * (HIST_SUB_BYTES / 4) + e;
+          unsigned l[HIST_CLUSTER], h[HIST_CLUSTER];
 #pragma unroll
-      for (int rep = 0; rep < (HIST_ROWS_SMEM / HIST_CLUSTER) * 32 / HIST_THREADS; ++rep) {
-        const int e = rank * (HIST_ROWS_SMEM / HIST_CLUSTER) * 32 + rep * HIST_THREADS + tid;  // column = tid & 31
-        const int b = e >> 5;
-        unsigned l[HIST_CLUSTER], h[HIST_CLUSTER];
+          for (int k = 0; k < HIST_CLUSTER; ++k) { l[k] = rlo[k][eo]; h[k] = rlo[k][eo + HIST_ROWS_SMEM * 32]; }
+          i64 v = 0;
 #pragma unroll
-        for (int k = 0; k < HIST_CLUSTER; ++k) { l[k] = rlo[k][e]; h[k] = rlo[k][e + HIST_ROWS_SMEM * 32]; }
-        i64 v = 0;
-#pragma unroll
-        for (int k = 0; k < HIST_CLUSTER; ++k) v += (i64)(((unsigned long long)h[k] << 32) | l[k]);
-        if (b < nslots && v) atomic_add_i64(dst + 2 * b, v);
+          for (int k = 0; k < HIST_CLUSTER; ++k) v += (i64)(((unsigned long long)h[k] << 32) | l[k]);
+          if (b < nslots && v) atomic_add_i64(dst + 2 * b, v);
+        }
       }
     }
     HSTAGE(3);

@@ -123,7 +123,7 @@ struct LgbCuContext {
   // tree state
   DevParams params{}; bool params_set = false;
   int alloc_leaves = 0;
-  int lookahead = LGB_KMAX, alloc_lookahead = 0, pool_slots = 0, last_rounds = 0;  // K leaves expanded per round (LGBCU_LOOKAHEAD)
+  int lookahead = LGB_KMAX, lookahead_cfg = 0, alloc_lookahead = 0, pool_slots = 0, last_rounds = 0;  // cfg 0 = choose from the data shape  // K leaves expanded per round (LGBCU_LOOKAHEAD)
   DevSpec* d_spec = nullptr; int* d_expanded = nullptr;
   long long bits_stride = 0; int part_sync_stride = 0;
   HistEntry* d_pool = nullptr;
@@ -192,7 +192,13 @@ int ensure_tree_buffers(LgbCuContext* c) {
   NEED(c->F > 0 && c->N > 0, "lgbcu: dataset not set");
   NEED(c->params_set, "lgbcu: tree params not set");
   const int L = c->params.num_leaves;
-  if (c->alloc_leaves == L && c->alloc_lookahead == c->lookahead && c->d_pool) return 0;
+  // K leaves expanded per round.  Every expanded leaf costs 2 x F blocks in the split search of its round whether or
+  // not its turn comes soon, so wide data gets a smaller K: about two resident waves of search blocks per round
+  // (measured best on 28-, 137- and 2000-feature shapes: K = 16, 4, 1).
+  int K = c->lookahead_cfg;
+  if (K <= 0) { K = c->num_sms * 4 / std::max(1, c->F); if (K < 1) K = 1; if (K > LGB_KMAX) K = LGB_KMAX; }
+  if (c->alloc_leaves == L && c->alloc_lookahead == K && c->d_pool) return 0;
+  c->lookahead = K;  // the memory guard below may lower it; alloc_lookahead remembers what was asked for
   drop_graph(c);
   CU(cudaSetDevice(c->device));
   // histogram slots: the root + one fresh slot per (round, item); a round commits at least one leaf, so there are at
@@ -219,7 +225,7 @@ int ensure_tree_buffers(LgbCuContext* c) {
   if (c->h_records) cudaFreeHost(c->h_records);
   CU(cudaMallocHost(reinterpret_cast<void**>(&c->h_records), sizeof(LgbCuSplitRecord) * (size_t)L));
   CU(cudaMemsetAsync(c->d_splittable, 0, slots * c->F, c->stream));
-  c->alloc_lookahead = c->lookahead;
+  c->alloc_lookahead = K;
   c->alloc_leaves = L;
   return 0;
 }
@@ -392,7 +398,7 @@ int lgbcu_create(int device_id, LgbCuContext** out) {
     // one slot per SM is left for the control block
     if (per_sm - 1 < c->part_blocks_per_sm) c->part_blocks_per_sm = per_sm - 1;
     if (const char* e = std::getenv("LGBCU_GRAPH")) c->use_graph = std::atoi(e) != 0;
-    if (const char* e = std::getenv("LGBCU_LOOKAHEAD")) { const int v = std::atoi(e); if (v >= 1 && v <= LGB_KMAX) c->lookahead = v; }
+    if (const char* e = std::getenv("LGBCU_LOOKAHEAD")) { const int v = std::atoi(e); if (v >= 1 && v <= LGB_KMAX) c->lookahead_cfg = v; }
     if (const char* e = std::getenv("LGBCU_GRAPH_COMM")) c->graph_comm = std::atoi(e) != 0;
     if (const char* e = std::getenv("LGBCU_FORCE_DP_COUNTS")) c->force_dp_counts = std::atoi(e) != 0;
   }

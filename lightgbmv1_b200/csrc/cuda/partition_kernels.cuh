@@ -144,6 +144,13 @@ __global__ void __launch_bounds__(PART_THREADS, PART_BLOCKS_PER_SM + 1) k_partit
   if (mode == 0) {
     const int ni = c->num_items;
     if (ni <= 0) return;
+    // the fresh histogram slots of this round's expansions (see part_expand) must be zero before k_hist adds to them:
+    // every block of the grid clears a slice of each, whether or not it owns tiles
+    for (int i = 0; i < ni; ++i) {
+      uint4* z = reinterpret_cast<uint4*>(V.pool + (size_t)(1 + (c->round - 1) * c->lookahead + i) * V.total_bin);
+      const uint4 zero = make_uint4(0, 0, 0, 0);
+      for (int k = blockIdx.x * PART_THREADS + threadIdx.x; k < V.total_bin; k += gridDim.x * PART_THREADS) z[k] = zero;
+    }
     // the grid's blocks are dealt to the items in proportion to their 1024-row tiles; one control block per item
     int tiles[LGB_KMAX];
     long long T = 0;
@@ -276,12 +283,6 @@ __global__ void __launch_bounds__(PART_THREADS, PART_BLOCKS_PER_SM + 1) k_partit
     if (mode == 0) {  // snapshot FeatureHistogram::is_splittable_ of the leaf being split for k_find_split
       const int8_t* sp = V.splittable + (size_t)L.slot * V.num_features;
       for (int f = tid; f < V.num_features; f += PART_THREADS) V.parent_split[(size_t)e * V.num_features + f] = sp[f];
-    }
-    if (mode == 0) {  // the fresh histogram slot of this expansion (see part_expand) must be zero before k_hist adds to it
-      const int fresh = 1 + (c->round - 1) * c->lookahead + e;
-      uint4* z = reinterpret_cast<uint4*>(V.pool + (size_t)fresh * V.total_bin);
-      const uint4 zero = make_uint4(0, 0, 0, 0);
-      for (int i = tid; i < V.total_bin; i += PART_THREADS) z[i] = zero;
     }
     if (tid == 0) {
       if (mode == 1) part_control_stepwise(V, leaf, L, total);
