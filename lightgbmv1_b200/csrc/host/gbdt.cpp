@@ -244,11 +244,14 @@ bool GBDT::TrainOneIter(const float* grad, const float* hess) {
 
 void GBDT::GetTrainScore(double* out, bool converted) const {
   const int N = train_->num_data();
+  StageTimer st;
   Check(lgbcu_copy_score(ctx_, out, N));
+  st.tick("copy scores to host");
   if (converted && objective_) {
 #pragma omp parallel for schedule(static)
     for (int i = 0; i < N; ++i) { double v = out[i]; objective_->ConvertOutput(&v, &out[i]); }
   }
+  st.tick("convert output");
 }
 
 // ---- validation data and metrics ----------------------------------------------------------------------------------
