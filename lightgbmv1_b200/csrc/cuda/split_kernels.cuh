@@ -4,13 +4,14 @@
 // SerialTreeLearner::FindBestSplitsFromHistograms, serial_tree_learner.cpp:358-425, and the leaf choice of
 // SerialTreeLearner::Train, serial_tree_learner.cpp:181-199).
 //
-// One block of two warps per feature: warp 0 scans the smaller leaf, warp 1 forms larger = parent - smaller
-// and scans it.  A warp holds the <=256 bins of a feature 8 per lane; the reference's sequential
-// accumulation becomes an exact integer warp prefix/suffix scan (the histogram is 64-bit fixed point), each
-// lane evaluates its 8 thresholds, and an argmax reduction applies the reference's tie-break (reverse scan
-// keeps the highest threshold among equal gains, forward scan the lowest; reverse wins ties with forward).
-// The last block to finish reduces over features (SplitInfo::operator>, split_info.hpp:126-153), then picks
-// the leaf to split next and writes the split descriptor the partition kernels read -- no host involved.
+// One 256-thread block per (feature, child of a leaf being expanded).  Block "sel 0" scans the smaller child, block
+// "sel 1" forms larger = parent - smaller in place and scans it.  Gradient sums and the reconstructed counts are exact
+// integer prefix / suffix scans (the histogram is 64-bit fixed point) done by half of the block, while the other half
+// replays the two kEpsilon-seeded hessian chains in the reference's order; each thread then evaluates one threshold,
+// and REDUX arg-max reductions apply the reference's tie-breaks (reverse scan keeps the highest threshold among equal
+// gains, forward scan the lowest; reverse wins ties with forward).  The last block to finish runs the control step:
+// per-leaf reduction over features (SplitInfo::operator>, split_info.hpp:126-153), commit of the expansions whose
+// turn has come in the reference's order, choice of the next round's leaves -- no host involved.
 #pragma once
 #include "dev_types.cuh"
 
@@ -500,7 +501,7 @@ __device__ void find_item(const DevView& V, ScanSmem& S, int f, int sel, const F
     const DevLeaf Ls = T.Ls;
     int used = V.feat_used[f] != 0;
     // a feature with no valid threshold in the parent is skipped in both children (serial_tree_learner.cpp:319-326);
-    // k_part_scan snapshotted the parent's flags, so sibling blocks cannot race on them
+    // k_partition snapshotted the parent's flags, so sibling blocks cannot race on them
     if (T.has_larger && T.parent_split) used = used && T.parent_split[f] != 0;
     const int nt = F.num_bin - F.offset;
     const double inv_g = c->inv_g, inv_h = c->inv_h;
