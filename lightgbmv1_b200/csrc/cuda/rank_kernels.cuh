@@ -13,7 +13,7 @@
 
 #define RANK_SIGMOID_BINS (1024 * 1024)
 #define RANK_MAX_POSITION 10000
-#define RANK_THREADS 256
+#define RANK_THREADS 128
 
 struct RankDev {
   const int* boundaries; const double* score; const float* label; const float* weight;
