@@ -71,49 +71,51 @@ __global__ void __launch_bounds__(RANK_THREADS) k_lambdarank(RankDev R, int max_
     const double my_gain = R.label_gain[my_label];
     const double my_disc = R.discount[r];
     float lam = 0.0f, hes = 0.0f;
-    for (int i = 0; i < cnt; ++i) {
-      if (i != r) {
-        // doc is "low" for high = rank i
-        const double high_score = s_score[i];
-        if (high_score == LGB_MIN_SCORE) continue;
-        const int high_label = s_label[i];
-        if (high_label <= my_label || my_score == LGB_MIN_SCORE) continue;
-        const double delta_score = high_score - my_score;
-        const double dcg_gap = R.label_gain[high_label] - my_gain;
-        const double paired_discount = fabs(R.discount[i] - my_disc);
-        double delta_pair_NDCG = dcg_gap * paired_discount * inverse_max_dcg;
-        if (use_norm_dist) delta_pair_NDCG /= (0.01f + fabs(delta_score));
-        double p_lambda = rank_sigmoid(R, delta_score);
-        double p_hessian = p_lambda * (1.0f - p_lambda);
-        p_lambda *= -R.sigmoid * delta_pair_NDCG;
-        p_hessian *= R.sigmoid * R.sigmoid * delta_pair_NDCG;
-        lam -= (float)p_lambda;
-        hes += (float)p_hessian;
-      } else {
-        // doc is "high": sum over all j in order, in double
-        if (my_score == LGB_MIN_SCORE) continue;
-        double high_sum_lambda = 0.0, high_sum_hessian = 0.0;
-        for (int j = 0; j < cnt; ++j) {
-          if (j == r) continue;
-          const int low_label = s_label[j];
-          const double low_score = s_score[j];
-          if (my_label <= low_label || low_score == LGB_MIN_SCORE) continue;
-          const double delta_score = my_score - low_score;
-          const double dcg_gap = my_gain - R.label_gain[low_label];
-          const double paired_discount = fabs(my_disc - R.discount[j]);
-          double delta_pair_NDCG = dcg_gap * paired_discount * inverse_max_dcg;
-          if (use_norm_dist) delta_pair_NDCG /= (0.01f + fabs(delta_score));
-          double p_lambda = rank_sigmoid(R, delta_score);
-          double p_hessian = p_lambda * (1.0f - p_lambda);
-          p_lambda *= -R.sigmoid * delta_pair_NDCG;
-          p_hessian *= R.sigmoid * R.sigmoid * delta_pair_NDCG;
-          high_sum_lambda += p_lambda;
-          high_sum_hessian += p_hessian;
-          local_sum -= 2 * p_lambda;
-        }
-        lam += (float)high_sum_lambda;
-        hes += (float)high_sum_hessian;
+    // One pair term.  Written without branches so that the table look-ups and divisions of neighbouring pairs overlap:
+    // a pair that the reference skips contributes exactly +0 (x - 0 == x and x + 0 == x bit for bit).
+    auto pair_term = [&](double high_score, int high_label, double high_disc, double low_score, int low_label,
+                         double low_disc, bool ok, double* pl, double* ph) {
+      const double delta_score = ok ? high_score - low_score : 0.0;
+      const double dcg_gap = R.label_gain[ok ? high_label : 0] - R.label_gain[ok ? low_label : 0];
+      const double paired_discount = fabs(high_disc - low_disc);
+      double delta_pair_NDCG = dcg_gap * paired_discount * inverse_max_dcg;
+      if (use_norm_dist) delta_pair_NDCG /= (0.01f + fabs(delta_score));
+      double p_lambda = rank_sigmoid(R, delta_score);
+      double p_hessian = p_lambda * (1.0f - p_lambda);
+      p_lambda *= -R.sigmoid * delta_pair_NDCG;
+      p_hessian *= R.sigmoid * R.sigmoid * delta_pair_NDCG;
+      *pl = ok ? p_lambda : 0.0;
+      *ph = ok ? p_hessian : 0.0;
+    };
+    const bool me_valid = my_score != LGB_MIN_SCORE;
+    // ranks before r: doc is the lower-labelled one of pair (i, r)
+#pragma unroll 4
+    for (int i = 0; i < r; ++i) {
+      const double hs = s_score[i]; const int hl = s_label[i];
+      double pl, ph;
+      pair_term(hs, hl, R.discount[i], my_score, my_label, my_disc, me_valid && hs != LGB_MIN_SCORE && hl > my_label, &pl, &ph);
+      lam -= (float)pl; hes += (float)ph;
+    }
+    // rank r itself: doc is the higher-labelled one; the reference sums these in double over all j, in order
+    {
+      double high_sum_lambda = 0.0, high_sum_hessian = 0.0;
+#pragma unroll 4
+      for (int j = 0; j < cnt; ++j) {
+        const double ls = s_score[j]; const int ll = s_label[j];
+        double pl, ph;
+        pair_term(my_score, my_label, my_disc, ls, ll, R.discount[j], me_valid && j != r && ls != LGB_MIN_SCORE && my_label > ll, &pl, &ph);
+        high_sum_lambda += pl; high_sum_hessian += ph;
+        local_sum -= 2 * pl;
       }
+      if (me_valid) { lam += (float)high_sum_lambda; hes += (float)high_sum_hessian; }
+    }
+    // ranks after r
+#pragma unroll 4
+    for (int i = r + 1; i < cnt; ++i) {
+      const double hs = s_score[i]; const int hl = s_label[i];
+      double pl, ph;
+      pair_term(hs, hl, R.discount[i], my_score, my_label, my_disc, me_valid && hs != LGB_MIN_SCORE && hl > my_label, &pl, &ph);
+      lam -= (float)pl; hes += (float)ph;
     }
     R.grad[start + s_doc[r]] = lam;
     R.hess[start + s_doc[r]] = hes;
