@@ -201,8 +201,13 @@ LGBCU_API int lgbcu_train_tree(LgbCuContext* ctx, LgbCuSplitRecord* records, int
 /* A11: data-parallel (src/treelearner/data_parallel_tree_learner.cpp) -- communicator plumbing.
  * unique_id is NCCL's 128-byte id; rank 0 creates it, the caller broadcasts it (torch.distributed / MPI / file). */
 LGBCU_API int lgbcu_comm_unique_id(uint8_t* id128);
+/* The communicator belongs to the rendezvous, not to the context (Network::Init is once per process in the reference,
+ * src/network/network.cpp:45-58): the first context naming (id, rank, world, device) creates it, later ones attach to
+ * the cached communicator; lgbcu_comm_destroy only detaches; lgbcu_comm_release_all destroys every cached
+ * communicator (call it when no context uses one any more: LGBM_NetworkFree). */
 LGBCU_API int lgbcu_comm_init(LgbCuContext* ctx, const uint8_t* id128, int32_t rank, int32_t world_size);
 LGBCU_API int lgbcu_comm_destroy(LgbCuContext* ctx);
+LGBCU_API int lgbcu_comm_release_all(void);
 /* small host-side syncs of the data-parallel path (Network::GlobalSyncUpBySum / ByMean, include/LightGBM/network.h:
  * 160-260): in-place sum over ranks of n <= 64 doubles.  No-op on one rank. */
 LGBCU_API int lgbcu_comm_allreduce_sum_f64(LgbCuContext* ctx, double* inout, int32_t n);
@@ -216,13 +221,14 @@ LGBCU_API int lgbcu_comm_allreduce_sum_f64(LgbCuContext* ctx, double* inout, int
  * refused with an error).  All pointers except `meta` are DEVICE pointers owned by the caller:
  *   bins_dev        row-major u8 matrix, `row_stride` bytes per row; `column` = byte of the split feature
  *   meta            (host) bin-mapper facts of that feature, as for lgbcu_set_dataset
- *   indices_in_dev  n row indices; indices_out_dev (a different buffer) receives the rows going left, in their
- *                   original order, followed by the rows going right, in their original order
+ *   indices_in_dev  n row indices; indices_out_dev (a buffer that does not overlap it, or the call is refused) receives
+ *                   the rows going left, in their original order, followed by the rows going right, in their order
  *   left_count_dev  one int32 on the device: number of rows that went left
  *   stream          cudaStream_t (NULL = default stream); the call only enqueues kernels and returns
  * Same decision rule as lgbcu_partition / DenseBin::SplitInner.  Calls share the built-in array: calls that can
- * overlap on one GPU race -- keep them on one stream.  The first call on a device resolves the array's address;
- * make it before any stream capture begins. */
+ * overlap on one GPU race -- keep them on one stream.  The first call on a device resolves the array's address
+ * (and caches it for the life of the process: a cudaDeviceReset() in between is not supported); make it before any
+ * stream capture begins. */
 #define LGBCU_NOALLOC_MAX_ROWS (1 << 22)
 LGBCU_API int lgbcu_partition_rows_noalloc(const uint8_t* bins_dev, int64_t row_stride, int32_t column,
                                            const LgbCuFeatureMeta* meta, int32_t threshold, int32_t default_left,

@@ -8,10 +8,12 @@
 #include <cstdio>
 #include <cstdlib>
 #include <cstring>
+#include <mutex>
 #include <string>
 #include <vector>
 
 #include <dlfcn.h>
+#include <omp.h>
 #include <sys/mman.h>
 #include <unistd.h>
 #include <nccl.h>
@@ -121,7 +123,7 @@ struct LgbCuContext {
   double* d_label_gain = nullptr; int num_label_gain = 0;
   double* d_inv_max_dcg = nullptr; float* d_sigmoid_table = nullptr;
   RankParams rank_params;
-  bool rank_ready = false;
+  bool rank_ready = false, rank_attr_set = false;
   // tree state
   DevParams params{}; bool params_set = false;
   int alloc_leaves = 0;
@@ -184,6 +186,15 @@ int grid_for(const LgbCuContext* c, long long work, int block, int per_sm = 8) {
   if (g > cap) g = cap;
   if (g < 1) g = 1;
   return (int)g;
+}
+
+// Threads for the library's own host-side copy loops.  A launcher may pin OMP_NUM_THREADS to 1 per rank (torchrun
+// does); the D2H staging copies are memory-bound helpers, not user compute, so they take a fair share of the cores.
+int host_copy_threads(const LgbCuContext* c) {
+  static const int hw = [] { const long n = sysconf(_SC_NPROCESSORS_ONLN); return n > 0 ? (int)n : 1; }();
+  if (const char* e = std::getenv("LGBM_B200_HOST_THREADS")) { const int v = std::atoi(e); if (v >= 1) return v; }
+  const int share = std::max(1, hw / std::max(1, c->world));
+  return std::max(omp_get_max_threads(), std::min(8, share));
 }
 
 void drop_graph(LgbCuContext* c) {
@@ -684,6 +695,7 @@ int lgbcu_copy_score(LgbCuContext* c, double* score, int32_t n) {
   // The caller's buffer is pageable (and usually untouched): stream the scores through two page-locked staging
   // buffers and let the host threads move each chunk on while the next one is in flight.
   const size_t CH = (size_t)1 << 19;  // doubles per chunk (4 MB)
+  const int nthreads = host_copy_threads(c);
   if ((size_t)n <= CH) {
     CU(cudaMemcpyAsync(score, c->d_score, sizeof(double) * n, cudaMemcpyDeviceToHost, c->stream));
     CU(cudaStreamSynchronize(c->stream));
@@ -701,7 +713,7 @@ int lgbcu_copy_score(LgbCuContext* c, double* score, int32_t n) {
     if (hi > lo) {
       const size_t slice = (size_t)8 << 20;
       const long long pieces = (long long)((hi - lo + slice - 1) / slice);
-#pragma omp parallel for schedule(static)
+#pragma omp parallel for schedule(static) num_threads(nthreads)
       for (long long p = 0; p < pieces; ++p) {
         const uintptr_t a = lo + (uintptr_t)p * slice, b = std::min<uintptr_t>(hi, a + slice);
         (void)madvise(reinterpret_cast<void*>(a), b - a, MADV_POPULATE_WRITE);
@@ -729,7 +741,7 @@ int lgbcu_copy_score(LgbCuContext* c, double* score, int32_t n) {
     double* dst = score + k * CH;
     const double* src = c->h_stage[cur];
     const long long pieces = (long long)((len + 32767) / 32768);
-#pragma omp parallel for schedule(static)
+#pragma omp parallel for schedule(static) num_threads(nthreads)
     for (long long p = 0; p < pieces; ++p) {
       const size_t a = (size_t)p * 32768, b = std::min(len, a + 32768);
       std::memcpy(dst + a, src + a, (b - a) * sizeof(double));
@@ -948,7 +960,8 @@ static int enqueue_round(LgbCuContext* c, int round, cudaEvent_t* ev) {
   if (launch_hist(c, -1)) return -1;
   if (c->comm) {  // slots of a round are a function of (round, item): the collective is enqueued blind
     const int first = round == 0 ? 0 : 1 + (round - 1) * K, count = round == 0 ? 1 : K;
-    if (first + count <= c->pool_slots && comm_reduce_hist(c, first, count)) return -1;
+    NEED(first + count <= c->pool_slots, "lgbcu_train_tree: round %d needs histogram slots [%d, %d) but the pool has %d", round, first, first + count, c->pool_slots);
+    if (comm_reduce_hist(c, first, count)) return -1;
   }
   if (round == 0) LAUNCH(k_root_sums, 1, 32, 0, c->stream, V);
   if (ev) CU(cudaEventRecord(ev[1], c->stream));
@@ -1116,16 +1129,41 @@ int lgbcu_comm_unique_id(uint8_t* id128) {
   return 0;
 }
 
+// NCCL communicators live as long as the rendezvous they belong to, not as long as a booster (the reference's
+// Network::Init runs once per process, src/network/network.cpp:45-58): the first context that names a (unique id,
+// rank, world, device) creates the communicator, later contexts attach to the cached one.  lgbcu_comm_release_all()
+// (LGBM_NetworkFree) destroys them; no context may still be using one then.
+struct CachedComm { uint8_t id[128]; int rank, world, device; ncclComm_t comm; };
+static std::vector<CachedComm> g_comms;
+static std::mutex g_comms_mu;
+
 int lgbcu_comm_init(LgbCuContext* c, const uint8_t* id128, int32_t rank, int32_t world_size) {
   NEED(c && id128, "lgbcu_comm_init: NULL argument");
   NEED(world_size >= 1 && rank >= 0 && rank < world_size, "lgbcu_comm_init: bad rank %d / world %d", rank, world_size);
   if (world_size == 1) { c->rank = 0; c->world = 1; return 0; }
   if (nccl_load()) return -1;
   CU(cudaSetDevice(c->device));
+  std::lock_guard<std::mutex> lock(g_comms_mu);
+  for (const CachedComm& k : g_comms) {
+    if (k.rank == rank && k.world == world_size && k.device == c->device && std::memcmp(k.id, id128, 128) == 0) {
+      c->comm = k.comm; c->rank = rank; c->world = world_size;
+      return 0;
+    }
+  }
   ncclUniqueId id;
   std::memcpy(&id, id128, 128);
-  NC(g_nccl.CommInitRank(&c->comm, world_size, id, rank));
-  c->rank = rank; c->world = world_size;
+  CachedComm k;
+  NC(g_nccl.CommInitRank(&k.comm, world_size, id, rank));
+  std::memcpy(k.id, id128, 128); k.rank = rank; k.world = world_size; k.device = c->device;
+  g_comms.push_back(k);
+  c->comm = k.comm; c->rank = rank; c->world = world_size;
+  return 0;
+}
+
+int lgbcu_comm_release_all(void) {
+  std::lock_guard<std::mutex> lock(g_comms_mu);
+  for (const CachedComm& k : g_comms) { cudaSetDevice(k.device); g_nccl.CommDestroy(k.comm); }
+  g_comms.clear();
   return 0;
 }
 
@@ -1141,10 +1179,10 @@ int lgbcu_comm_allreduce_sum_f64(LgbCuContext* c, double* inout, int32_t n) {
   return 0;
 }
 
-int lgbcu_comm_destroy(LgbCuContext* c) {
+int lgbcu_comm_destroy(LgbCuContext* c) {  // detach: the communicator itself stays cached (see lgbcu_comm_init)
   if (!c || !c->comm) return 0;
-  g_nccl.CommDestroy(c->comm);
   c->comm = nullptr; c->world = 1; c->rank = 0;
+  drop_graph(c);
   return 0;
 }
 

@@ -140,22 +140,24 @@ __global__ void __launch_bounds__(PART_THREADS) k_na_scatter(const int* __restri
 }
 
 // device address of the scratch array, looked up once per device
-unsigned int* g_na_addr[64] = {nullptr};
-std::atomic<int> g_na_ready[64];
+// (an atomic pointer per device: concurrent first calls may both resolve it, and both store the same value; a
+// cudaDeviceReset() invalidates the cached address -- this library does not support being used across one)
+std::atomic<unsigned int*> g_na_addr[64];
 
 int noalloc_scratch(unsigned int** out) {
   int dev = 0;
   CU(cudaGetDevice(&dev));
   NEED(dev >= 0 && dev < 64, "lgbcu_partition_rows_noalloc: device index %d out of range", dev);
-  if (!g_na_ready[dev].load(std::memory_order_acquire)) {
+  unsigned int* cached = g_na_addr[dev].load(std::memory_order_acquire);
+  if (!cached) {
     void* p = nullptr;
     // with `dev` current this yields THAT device's copy of the array; the host-side symbol itself is not an address
     CU(cudaGetSymbolAddress(&p, g_noalloc_scratch));
     NEED(p != nullptr, "lgbcu_partition_rows_noalloc: cudaGetSymbolAddress returned NULL");
-    g_na_addr[dev] = static_cast<unsigned int*>(p);
-    g_na_ready[dev].store(1, std::memory_order_release);
+    cached = static_cast<unsigned int*>(p);
+    g_na_addr[dev].store(cached, std::memory_order_release);
   }
-  *out = g_na_addr[dev];
+  *out = cached;
   return 0;
 }
 
@@ -170,7 +172,8 @@ extern "C" int lgbcu_partition_rows_noalloc(const uint8_t* bins_dev, int64_t row
   NEED(n <= LGBCU_NOALLOC_MAX_ROWS, "lgbcu_partition_rows_noalloc: %d rows exceed the built-in scratch (at most %d rows "
        "per call); partition in pieces or use lgbcu_partition", n, LGBCU_NOALLOC_MAX_ROWS);
   NEED(row_stride > 0 && column >= 0 && column < row_stride, "lgbcu_partition_rows_noalloc: column %d outside the row stride", column);
-  NEED(indices_in_dev != indices_out_dev, "lgbcu_partition_rows_noalloc: input and output index buffers must differ");
+  NEED(indices_in_dev + n <= indices_out_dev || indices_out_dev + n <= indices_in_dev,
+       "lgbcu_partition_rows_noalloc: input and output index buffers must not overlap");
   NEED(meta->num_bin >= 1 && meta->most_freq_bin >= 0 && meta->most_freq_bin < meta->num_bin, "lgbcu_partition_rows_noalloc: bad feature meta");
   unsigned int* scratch = nullptr;
   if (noalloc_scratch(&scratch)) return -1;

@@ -180,7 +180,9 @@ __global__ void __launch_bounds__(PART_THREADS, PART_BLOCKS_PER_SM + 1) k_partit
   const DevLeaf L = V.leaves[leaf];
   const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
   const int ntiles = (L.count + PART_TILE - 1) / PART_TILE;
-  const int tpb = (ntiles + maxp - 1) / maxp;          // tiles per block
+  // an empty leaf (possible on one rank of a data-parallel run: none of a globally splittable leaf's rows live in this
+  // shard) owns no tiles: P = 0, block 0 is the control block and records left_count = 0
+  const int tpb = max(1, (ntiles + maxp - 1) / maxp);  // tiles per block
   const int P = (ntiles + tpb - 1) / tpb;              // blocks that own tiles
   if (bid > P) return;
   const bool control = bid == P;

@@ -228,10 +228,9 @@ int rank_launch(LgbCuContext* c) {
   R.norm = c->rank_params.norm;
   const size_t smem = (size_t)c->max_query * (sizeof(double) + 2 * sizeof(int));
   NEED(smem <= 200 * 1024, "lambdarank: query of %d documents does not fit the per-query shared memory tile", c->max_query);
-  static bool attr_set = false;
-  if (!attr_set) {
+  if (!c->rank_attr_set) {  // the attribute is per device: kept per context, not per process
     CU(cudaFuncSetAttribute(k_lambdarank, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024));
-    attr_set = true;
+    c->rank_attr_set = true;
   }
   LAUNCH(k_lambdarank, c->num_queries, RANK_THREADS, smem, c->stream, R, c->max_query);
   return 0;

@@ -268,6 +268,7 @@ int LGBM_NetworkInitNCCL(const uint8_t* id128, int rank, int num_machines) {
 
 int LGBM_NetworkFree(void) {
   API_BEGIN();
+  lgbcu_comm_release_all();  // boosters that trained over it must have been freed (as with Network::Dispose)
   Net() = NetworkState();
   API_END();
 }

@@ -41,18 +41,23 @@ GBDT::GBDT(const Dataset* train, const Config& config)
   if (F <= 0) Log::Fatal("the CUDA learner needs at least one non-constant feature");
   StageTimer st;
   objective_.reset(Objective::Create(config_));
-  if (objective_) {
-    objective_->Init(train_->metadata(), N);
-    class_need_train_ = objective_->NeedTrain();
-  }
   // ---- device learner (TreeLearner::Init + ScoreUpdater ctor, gbdt.cpp:78-91)
   int ndev = 0;
   lgbcu_device_count(&ndev);
   int dev = config_.gpu_device_id >= 0 ? config_.gpu_device_id : 0;
   if (Net().active && config_.gpu_device_id < 0 && ndev > 0) dev = Net().rank % ndev;
-  st.tick("objective init");
   Check(lgbcu_create(dev, &ctx_));
   st.tick("lgbcu_create");
+  // the communicator comes first: the objective's Init sums class counts over the machines
+  if (Net().active && Net().num_machines > 1 && config_.tree_learner == "data") {
+    Check(lgbcu_comm_init(ctx_, Net().unique_id, Net().rank, Net().num_machines));
+  }
+  if (objective_) {
+    LgbCuContext* ctx = ctx_;
+    objective_->Init(train_->metadata(), N, [ctx](double* v, int n) { Check(lgbcu_comm_allreduce_sum_f64(ctx, v, n)); });
+    class_need_train_ = objective_->NeedTrain();
+  }
+  st.tick("comm + objective init");
   std::vector<LgbCuFeatureMeta> meta(F);
   for (int f = 0; f < F; ++f) {
     const BinMapper& m = train_->mapper(f);
@@ -80,9 +85,6 @@ GBDT::GBDT(const Dataset* train, const Config& config)
     Check(lgbcu_set_query(ctx_, md.query_boundaries.data(), static_cast<int>(md.query_boundaries.size()) - 1));
   if (objective_) objective_->Configure(ctx_);
   if (!md.init_score.empty()) { Check(lgbcu_set_score(ctx_, md.init_score.data(), N)); has_init_score_ = true; }
-  if (Net().active && Net().num_machines > 1 && config_.tree_learner == "data") {
-    Check(lgbcu_comm_init(ctx_, Net().unique_id, Net().rank, Net().num_machines));
-  }
   records_.resize(std::max(config_.num_leaves - 1, 1));
   st.tick("labels/objective/comm");
   // ---- metrics (Metric::CreateMetric, src/metric/metric.cpp:16-63; "custom" yields none)

@@ -16,16 +16,21 @@ class BinaryLogloss : public Objective {
     if (sigmoid_ <= 0.0) Log::Fatal("Sigmoid parameter %f should be greater than zero", sigmoid_);
     if (is_unbalance_ && std::fabs(scale_pos_weight_ - 1.0f) > 1e-6) Log::Fatal("Cannot set is_unbalance and scale_pos_weight at the same time");
   }
-  void Init(const Metadata& meta, data_size_t n) override {
+  void Init(const Metadata& meta, data_size_t n, const SumSync& sum_over_ranks) override {
     num_data_ = n; label_ = meta.label.data(); weights_ = meta.weights.empty() ? nullptr : meta.weights.data();
     if (meta.label.empty()) Log::Fatal("Label should not be NULL");
-    data_size_t pos = 0, neg = 0;
+    long long pos = 0, neg = 0;
 #pragma omp parallel for schedule(static) reduction(+:pos, neg)
     for (data_size_t i = 0; i < n; ++i) { if (label_[i] > 0) ++pos; else ++neg; }
-    num_pos_ = pos;
+    num_pos_ = static_cast<data_size_t>(pos);
+    {  // binary_objective.hpp:72-75: the class counts of ALL machines decide need_train_ and the label weights
+      double cnt[2] = {static_cast<double>(pos), static_cast<double>(neg)};  // counts < 2^53: exact as doubles
+      sum_over_ranks(cnt, 2);
+      pos = static_cast<long long>(cnt[0]); neg = static_cast<long long>(cnt[1]);
+    }
     need_train_ = !(neg == 0 || pos == 0);
     if (!need_train_) Log::Warning("Contains only one class");
-    Log::Info("Number of positive: %d, number of negative: %d", pos, neg);
+    Log::Info("Number of positive: %lld, number of negative: %lld", pos, neg);
     label_weights_[0] = label_weights_[1] = 1.0f;
     if (is_unbalance_ && pos > 0 && neg > 0) {
       if (pos > neg) { label_weights_[1] = 1.0f; label_weights_[0] = static_cast<double>(pos) / neg; }
@@ -69,7 +74,7 @@ class RegressionL2 : public Objective {
   explicit RegressionL2(const Config& c) {
     if (c.reg_sqrt) Log::Fatal("reg_sqrt is outside this library's path");
   }
-  void Init(const Metadata& meta, data_size_t n) override {
+  void Init(const Metadata& meta, data_size_t n, const SumSync&) override {
     num_data_ = n; label_ = meta.label.data(); weights_ = meta.weights.empty() ? nullptr : meta.weights.data();
     if (meta.label.empty()) Log::Fatal("Label should not be NULL");
   }
@@ -101,7 +106,7 @@ class Lambdarank : public Objective {
       : sigmoid_(c.sigmoid), norm_(c.lambdarank_norm), trunc_(c.lambdarank_truncation_level), label_gain_(c.label_gain) {
     if (sigmoid_ <= 0.0) Log::Fatal("Sigmoid param %f should be greater than zero", sigmoid_);
   }
-  void Init(const Metadata& meta, data_size_t) override {
+  void Init(const Metadata& meta, data_size_t, const SumSync&) override {
     if (meta.query_boundaries.empty()) Log::Fatal("Ranking tasks require query information");
   }
   void Configure(LgbCuContext* ctx) const override {

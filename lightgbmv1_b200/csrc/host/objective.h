@@ -3,6 +3,7 @@
 // regression_objective.hpp:93-199, rank_objective.hpp:100-140).  GetGradients itself runs on device
 // (lgbcu_get_gradients); this class only derives its parameters.
 #pragma once
+#include <functional>
 #include <memory>
 #include <string>
 
@@ -16,7 +17,10 @@ class Objective {
  public:
   static Objective* Create(const Config& config);  // ObjectiveFunction::CreateObjectiveFunction
   virtual ~Objective() {}
-  virtual void Init(const Metadata& meta, data_size_t num_data) = 0;
+  // `sum_over_ranks` sums n doubles over the machines of a data-parallel run in place (Network::GlobalSyncUpBySum);
+  // it is a no-op on one machine
+  typedef std::function<void(double*, int)> SumSync;
+  virtual void Init(const Metadata& meta, data_size_t num_data, const SumSync& sum_over_ranks) = 0;
   virtual void Configure(LgbCuContext* ctx) const = 0;  // push kind + parameters to the device learner
   virtual double BoostFromScore() const = 0;
   virtual bool NeedTrain() const { return true; }

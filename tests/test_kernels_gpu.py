@@ -234,6 +234,25 @@ def test_partition_nested_keeps_order(orc):
     L.close()
 
 
+def test_partition_of_an_empty_leaf(orc):
+    # a leaf with no local rows (one rank of a data-parallel run can hold none of a leaf's rows): the partition must
+    # finish, report 0 rows on both sides and leave the other leaves alone -- step-wise API and whole-tree growth
+    n, F = 5_000, 4
+    rng, metas, bins, g, h = _make_case(310, n, F, kinds=[1])
+    L = N.CudaLearner()
+    L.set_dataset(bins, metas)
+    L.set_tree_params(N.make_tree_params(num_leaves=8))
+    L.set_gradients(g, h)
+    L.begin_tree()
+    nb = metas[0][0]
+    left = L.partition(0, 0, nb - 1, 1, 1)      # threshold = last bin: every row goes left, leaf 1 is empty
+    assert left == n and len(L.leaf_indices(1)) == 0
+    left2 = L.partition(1, 1, 0, 1, 2)          # split the empty leaf
+    assert left2 == 0 and len(L.leaf_indices(1)) == 0 and len(L.leaf_indices(2)) == 0
+    assert np.array_equal(L.leaf_indices(0), np.arange(n, dtype=np.int32))
+    L.close()
+
+
 def _orc_train(orc, bins, metas, params, g, h, bag=None, used=None):
     fm = N.make_feature_meta(metas)
     recs = (N.SplitRecord * max(params.num_leaves - 1, 1))()

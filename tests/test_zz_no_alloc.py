@@ -69,6 +69,14 @@ def test_noalloc_partition_matches_lgbcu_partition_twice_in_a_row():
         assert 0 < want_left < len(rows)
         assert got_left == want_left
         assert np.array_equal(got, want)
+        # and first-hand against the CPU oracle (DenseBin::SplitInner restated, oracle/oracle.c) on the same rows
+        orc = H.load_oracle()
+        lte = np.empty(len(rows), dtype=np.int32); gt = np.empty(len(rows), dtype=np.int32)
+        o_left = orc.orc_partition(H.fptr(bins, C.c_uint8), C.c_int(F), fm, C.c_int(feature), C.c_int(threshold),
+                                   C.c_int(default_left), H.fptr(rows, C.c_int32), C.c_int(len(rows)),
+                                   H.fptr(lte, C.c_int32), H.fptr(gt, C.c_int32))
+        assert got_left == o_left
+        assert np.array_equal(got, np.concatenate([lte[:o_left], gt[:len(rows) - o_left]]))
 
 
 def test_noalloc_partition_rejects_oversize_and_bad_arguments():
@@ -87,3 +95,9 @@ def test_noalloc_partition_rejects_oversize_and_bad_arguments():
     rc = fn(None, C.c_int64(16), C.c_int32(0), C.byref(fm[0]), C.c_int32(3), C.c_int32(0), C.c_void_p(buf.data_ptr()),
             C.c_int32(4), C.c_void_p(buf.data_ptr() + 128), C.c_void_p(buf.data_ptr() + 64), C.c_void_p(0))
     assert rc == -1
+    # partially overlapping input / output ranges are refused, not silently corrupted
+    rc = fn(C.c_void_p(b8.data_ptr()), C.c_int64(16), C.c_int32(0), C.byref(fm[0]), C.c_int32(3), C.c_int32(0),
+            C.c_void_p(buf.data_ptr()), C.c_int32(8), C.c_void_p(buf.data_ptr() + 16), C.c_void_p(buf.data_ptr() + 192),
+            C.c_void_p(0))
+    assert rc == -1
+    assert "overlap" in N.lib.lgbcu_last_error().decode()
