@@ -14,17 +14,23 @@ A "step" is one boosting iteration (gradients -> 254 x {histogram, split search,
            split records, bracketed by barrier + device sync, max over ranks.
 `e2e`    : the same K iterations INCLUDING LGBM_BoosterCreate (host->device upload of the binned matrix + labels)
            and a final LGBM_BoosterGetPredict (device->host read of all training scores), divided by K:
-           what a C-API user pays from host buffers.  h2d/d2h bytes are per step (total / K).
-`roofline`: the histogram kernel k_hist, algorithmic bytes per SURVEY 8(d)
-           (n*(G+8) [+4n if indexed] + total_bin*16 per call) over their CUDA-event time on the launch stream,
-           measured in a separate profiled pass after the timed region.
+           what a C-API user pays from host buffers.  h2d/d2h bytes are per step (total / K).  The data-parallel
+           rendezvous (LGBM_NetworkInitNCCL) is made once per process, as the reference's Network::Init is.
+`roofline`: the histogram kernel k_hist ALONE (CUDA events around the kernel, not around the all-reduce that follows
+           it in data-parallel runs), algorithmic bytes per SURVEY 8(d) (n*(G+8) [+4n if indexed] + total_bin*16 per
+           call), measured in a separate profiled pass after the timed region.
 `cpu_baseline`: the reference CPU learner timed here on the box's host cores on the same workload (few iterations).
+`train_check`: N = 1: the model the reference CPU learner grows in those iterations against the model this library
+           grows from the same start -- trees compared / identical, first mismatch, largest score difference.
+           N > 1: the N-rank model against the 1-rank model grown on the unsharded matrix with the data-parallel count
+           semantics (must be identical: the histogram all-reduce is an integer sum) and the agreement of all ranks.
 
 Multi-GPU (torchrun, one rank per GPU): STRONG scaling of the same 10.5M-row workload, rows sharded contiguously,
-tree_learner=data, one NCCL int64 all-reduce of the smaller leaf's histogram per split.
+tree_learner=data, one NCCL int64 all-reduce of the round's fresh histograms per round of tree growth.
 """
 import argparse
 import ctypes as C
+import hashlib
 import json
 import os
 import subprocess
@@ -48,27 +54,13 @@ ROOT = os.path.dirname(os.path.abspath(__file__))
 sys.path.insert(0, ROOT)
 sys.path.insert(0, os.path.join(ROOT, "tests"))
 
-PARAMS = ("objective=binary max_bin=255 num_leaves=255 learning_rate=0.1 min_data_in_leaf=0 "
-          "min_sum_hessian_in_leaf=100 verbosity=-1")
+import workloads as W  # noqa: E402
+
+PARAMS = W.HIGGS_PARAMS
 N_ROWS, N_FEAT = 10_500_000, 28
-
-
-def higgs_shaped(n, seed=0):
-    """SURVEY.md 8(d) config #2 generator: 21 gaussian, 4 half-zero, 3 three-level columns."""
-    rng = np.random.default_rng(seed)
-    X = np.empty((n, N_FEAT), dtype=np.float32)
-    chunk = 1 << 20
-    w = np.random.default_rng(seed + 1).standard_normal(N_FEAT).astype(np.float32)
-    y = np.empty(n, dtype=np.float32)
-    levels = np.array([0.0, 1.087, 2.173], dtype=np.float32)
-    for s in range(0, n, chunk):
-        e = min(n, s + chunk)
-        b = rng.standard_normal((e - s, N_FEAT), dtype=np.float32)
-        b[:, 21:25] = np.maximum(0, b[:, 21:25])
-        b[:, 25:28] = levels[rng.integers(0, 3, size=(e - s, 3))]
-        X[s:e] = b
-        y[s:e] = ((b @ w + 0.5 * b[:, 0] * b[:, 1] + rng.standard_normal(e - s, dtype=np.float32)) > 0)
-    return X, y
+higgs_shaped = W.higgs_shaped
+PARITY_ITERS = 10   # iterations compared tree by tree with the reference CPU learner (N = 1)
+DP_CHECK_ITERS = 5  # iterations of the N-rank == 1-rank check (N > 1)
 
 
 class ClockSampler:
@@ -118,6 +110,16 @@ def dist_env():
     return rank, world, local
 
 
+def workload_name(n):
+    return f"Higgs-shaped {n}x{N_FEAT} dense, max_bin=255, num_leaves=255, binary, lr 0.1 (configs[1])"
+
+
+def config_of(n):
+    """identical in both arms (the driver compares the dicts)"""
+    return {"workload": workload_name(n), "params": PARAMS,
+            "l2_note": "inputs larger than L2 (binned matrix ~300 MB + gradients / scores per pass)"}
+
+
 def run_reference(args):
     """The reference's own CPU implementation of the path (oracle/_ref), all host threads, same config."""
     rank, world, _ = dist_env()
@@ -146,14 +148,17 @@ def run_reference(args):
         "impl": "reference", "metric": "boosting iters/sec", "value": v, "unit": "iters/s", "n_gpus": args.gpus,
         "steps": args.steps, "warmup": args.warmup, "ms_per_step": 1e3 * dt / args.steps, "higher_is_better": True,
         "scaling": "strong", "vs_baseline": None, "dtype": "f64", "data": "synthetic",
-        "config": {"workload": f"Higgs-shaped {n}x{N_FEAT} dense, max_bin=255, num_leaves=255, binary, lr 0.1 (configs[1])",
-                   "params": PARAMS, "l2_note": "inputs larger than L2"},
+        "config": config_of(n),
         "cpu_baseline": {"value": v, "unit": "iters/s", "cores": cores, "kind": "reference",
                          "sample": f"full workload, {args.steps} iterations after {args.warmup} warm-up, force_col_wise"},
         "e2e": {"value": v, "unit": "iters/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
     }
     emit(line)
     return 0
+
+
+def model_hash(text):
+    return int(hashlib.sha256(text.split("feature_importances")[0].encode()).hexdigest()[:15], 16)
 
 
 def run_ours(args):
@@ -163,6 +168,8 @@ def run_ours(args):
     lib = ours.lib
     lib.LGBM_B200_LaunchCount.restype = C.c_int64
     use_dist = world > 1
+    cores = os.cpu_count() or 1
+    host_threads = max(1, cores // world)   # torchrun pins OMP_NUM_THREADS=1: ask for this rank's share of the cores
     if use_dist:
         import torch
         import torch.distributed as dist
@@ -170,7 +177,8 @@ def run_ours(args):
         dist.init_process_group("nccl")
     n = args.rows
     X, y = higgs_shaped(n)
-    ds_params = PARAMS
+    ds_params = PARAMS + f" num_threads={host_threads}"
+    ds_full = None
     if use_dist:
         # identical bin mappers on every rank: a reference dataset from the first 200k rows, then this rank's shard
         ref_ds = ours.dataset_from_mat(X[:200_000], ds_params)
@@ -178,38 +186,42 @@ def run_ours(args):
         Xs, ys = np.ascontiguousarray(X[lo:hi]), np.ascontiguousarray(y[lo:hi])
         ds = ours.dataset_from_mat(Xs, ds_params, reference=ref_ds)
         ours.set_field(ds, "label", ys)
-        def net_init():
-            # a fresh NCCL id per communicator (= per booster): rank 0 creates it, torch.distributed carries it
-            uid = np.zeros(128, dtype=np.uint8)
-            if rank == 0:
-                ours.check(lib.LGBM_NetworkGetNCCLUniqueId(uid.ctypes.data_as(C.POINTER(C.c_uint8))))
-            t = torch.from_numpy(uid).cuda()
-            dist.broadcast(t, 0)
-            uid = t.cpu().numpy()
-            ours.check(lib.LGBM_NetworkInitNCCL(uid.ctypes.data_as(C.POINTER(C.c_uint8)), C.c_int(rank), C.c_int(world)))
-        params = PARAMS + f" tree_learner=data num_machines={world} gpu_device_id={local}"
+        if rank == 0:   # the unsharded matrix with the same mappers, for the N-rank == 1-rank check
+            ds_full = ours.dataset_from_mat(X, ds_params, reference=ref_ds)
+            ours.set_field(ds_full, "label", y)
+        # the rendezvous is made ONCE per process (the reference's Network::Init, src/network/network.cpp:45-58):
+        # rank 0 creates the NCCL id, torch.distributed carries it; every booster of this process trains over it
+        uid = np.zeros(128, dtype=np.uint8)
+        if rank == 0:
+            ours.check(lib.LGBM_NetworkGetNCCLUniqueId(uid.ctypes.data_as(C.POINTER(C.c_uint8))))
+        t = torch.from_numpy(uid).cuda()
+        dist.broadcast(t, 0)
+        uid = t.cpu().numpy()
+        ours.check(lib.LGBM_NetworkInitNCCL(uid.ctypes.data_as(C.POINTER(C.c_uint8)), C.c_int(rank), C.c_int(world)))
+        params = ds_params + f" tree_learner=data num_machines={world} gpu_device_id={local}"
         local_rows = hi - lo
     else:
         ds = ours.dataset_from_mat(X, ds_params)
         ours.set_field(ds, "label", y)
-        params = PARAMS + f" gpu_device_id={local}"
+        params = ds_params + f" gpu_device_id={local}"
         local_rows = n
-
-        def net_init():
-            pass
-    del X
+    if not (world == 1 and not args.no_cpu_baseline):
+        del X
 
     def barrier():
         if use_dist:
             torch.cuda.synchronize()
             dist.barrier()
 
-    # one-time process cost (CUDA context + module load) is paid before any timing
+    # one-time process cost (CUDA context + module load, NCCL communicator) is paid before any timing
     from lightgbmv1_b200 import _native as _N
     _N.CudaLearner(local).close()
+    if use_dist:
+        b = ours.booster_create(ds, params)
+        ours.update(b)
+        ours.booster_free(b)
 
     # ---- e2e pass: BoosterCreate (H2D of the binned matrix + labels) + K iterations + GetPredict (D2H scores)
-    net_init()
     barrier()
     t0 = time.perf_counter()
     b = ours.booster_create(ds, params)
@@ -218,13 +230,12 @@ def run_ours(args):
     scores = ours.get_predict(b, local_rows)
     barrier()
     e2e_dt = time.perf_counter() - t0
-    row_stride = (N_FEAT + 15) // 16 * 16
     h2d_total = local_rows * (N_FEAT + 4)  # binned matrix (as passed by the host) + float labels
     d2h_total = local_rows * 8
     ours.booster_free(b)
+    del scores
 
     # ---- timed pass: W warm-up + exactly K iterations, device-resident
-    net_init()
     b = ours.booster_create(ds, params)
     for _ in range(args.warmup):
         ours.update(b)
@@ -250,74 +261,114 @@ def run_ours(args):
     ours.check(lib.LGBM_B200_BoosterProfile(b, 1, 1, C.byref(hist_ms), C.byref(hist_calls), C.byref(hist_bytes)))
     prof_iters = 3
     hist_launches = 0
+    phases = np.zeros(8)
     ph = (C.c_double * 8)()
     for _ in range(prof_iters):
         ours.update(b)
         ours.check(lib.LGBM_B200_BoosterPhases(b, ph))
         hist_launches += int(ph[7])   # rounds the tree needed = k_hist launches that did work (each covers up to 16 leaves)
+        phases += np.array(list(ph))
     ours.check(lib.LGBM_B200_BoosterProfile(b, 0, 0, C.byref(hist_ms), C.byref(hist_calls), C.byref(hist_bytes)))
+    ours.booster_free(b)
     peaks = {}
     try:
         peaks = json.load(open(os.path.join(ROOT, "MEASURED_PEAKS.json")))
     except Exception:
         pass
     peak = float(peaks.get("hbm_gbs", 6650.0))
-    # DRAM traffic of the histogram kernel per launch: from the committed ncu pass over one tree of this very workload
-    # (profiles/hist_traffic.json, written by tools/summarize_traffic.py from the ncu csv next to it)
-    traffic = None
-    try:
-        traffic = float(json.load(open(os.path.join(ROOT, "profiles", "hist_traffic.json")))["dram_bytes_per_launch"])
-    except Exception:
-        pass
     achieved = (hist_bytes.value / 1e9) / (hist_ms.value / 1e3) if hist_ms.value > 0 else 0.0
 
+    # ---- train_check
+    check = {}
+    check_params = params + " boost_from_average=false"
     if use_dist:
+        # (a) the N-rank model; (b) rank 0 alone on the unsharded matrix, same mappers, data-parallel count semantics
+        b = ours.booster_create(ds, check_params)
+        for _ in range(DP_CHECK_ITERS):
+            ours.update(b)
+        text_dp = ours.model_string(b)
         ours.booster_free(b)
+        h = model_hash(text_dp)
+        th = torch.tensor([h], dtype=torch.int64, device="cuda")
+        lst = [torch.zeros_like(th) for _ in range(world)]
+        dist.all_gather(lst, th)
+        ranks_agree = all(int(x) == h for x in lst)
+        if rank == 0:
+            os.environ["LGBCU_FORCE_DP_COUNTS"] = "1"
+            b1 = ours.booster_create(ds_full, ds_params + f" tree_learner=serial gpu_device_id={local} boost_from_average=false")
+            del os.environ["LGBCU_FORCE_DP_COUNTS"]
+            for _ in range(DP_CHECK_ITERS):
+                ours.update(b1)
+            text_1 = ours.model_string(b1)
+            ours.booster_free(b1)
+            same, ntrees, first = capi.compare_models(text_1, text_dp, rtol_value=0.0)
+            check = {"kind": f"{world}-rank data-parallel model vs 1-rank model on the unsharded matrix (data-parallel count "
+                             "semantics, same bin mappers, boost_from_average=false)",
+                     "trees_compared": ntrees, "trees_identical": same, "first_mismatch": first,
+                     "dp_equals_single": bool(same == ntrees and ntrees == DP_CHECK_ITERS), "all_ranks_agree": bool(ranks_agree)}
         dist.barrier()
+        ours.check(lib.LGBM_NetworkFree())
         dist.destroy_process_group()
     if rank != 0:
         return 0
-    # ---- cpu_baseline (N=1 only): the reference CPU learner on the same workload, few iterations
+    # ---- cpu_baseline (N=1 only): the reference CPU learner on the same workload, few iterations; its model is kept
     cpu = None
     if world == 1 and not args.no_cpu_baseline and os.path.exists(capi.REF_SO):
-        cores = os.cpu_count() or 1
-        Xc, yc = higgs_shaped(n)
         ref = capi.reference()
         rp = PARAMS + f" force_col_wise=true num_threads={cores}"
-        rds = ref.dataset_from_mat(Xc, rp)
-        ref.set_field(rds, "label", yc)
+        rds = ref.dataset_from_mat(X, rp)
+        ref.set_field(rds, "label", y)
         rb = ref.booster_create(rds, rp)
         ref.update(rb)
-        k = 3
+        k = PARITY_ITERS - 1
         t0 = time.perf_counter()
         for _ in range(k):
             ref.update(rb)
         cdt = time.perf_counter() - t0
         cpu = {"value": k / cdt, "unit": "iters/s", "cores": cores, "kind": "reference",
                "sample": f"same {n}x{N_FEAT} matrix and parameters, {k} iterations after 1 warm-up, force_col_wise, all host threads"}
+        text_ref = ref.model_string(rb)
+        pred_ref = ref.get_predict(rb, n)
+        ref.booster_free(rb); ref.dataset_free(rds)
+        b = ours.booster_create(ds, params)
+        for _ in range(PARITY_ITERS):
+            ours.update(b)
+        text_ours = ours.model_string(b)
+        pred_ours = ours.get_predict(b, n)
+        ours.booster_free(b)
+        same, ntrees, first = capi.compare_models(text_ref, text_ours, rtol_value=1e-9)
+        p0 = np.clip(pred_ref, 1e-15, 1 - 1e-15); p1 = np.clip(pred_ours, 1e-15, 1 - 1e-15)
+        ll = lambda p: float(-np.mean(y * np.log(p) + (1 - y) * np.log(1 - p)))
+        check = {"kind": "reference CPU learner (oracle/_ref) vs this library, same matrix, same start",
+                 "trees_compared": ntrees, "trees_identical": same, "first_mismatch": first,
+                 "max_abs_score_diff": float(np.max(np.abs(pred_ref - pred_ours))),
+                 "logloss_reference": ll(p0), "logloss_ours": ll(p1)}
     line = {
         "metric": "boosting iters/sec", "value": args.steps / dt, "unit": "iters/s", "n_gpus": world,
         "steps": args.steps, "warmup": args.warmup, "ms_per_step": 1e3 * dt / args.steps, "higher_is_better": True,
         "scaling": "strong", "vs_baseline": None, "dtype": "int64 fixed-point histograms / f64 split search",
         "data": "synthetic",
-        "config": {"workload": f"Higgs-shaped {n}x{N_FEAT} dense, max_bin=255, num_leaves=255, binary, lr 0.1 (configs[1])",
-                   "params": PARAMS, "parallelism": f"data-parallel x{world}" if world > 1 else "single GPU",
-                   "l2_note": "inputs larger than L2 (binned matrix 336 MB + 168 MB of gradients/scores per pass)"},
+        "config": config_of(n),
+        "parallelism": f"data-parallel x{world} (rows sharded, NCCL)" if world > 1 else "single GPU",
         "clocks": clocks,
         "e2e": {"value": args.steps / e2e_dt, "unit": "iters/s", "h2d_bytes_per_step": h2d_total / args.steps,
                 "d2h_bytes_per_step": d2h_total / args.steps,
                 "what": "LGBM_BoosterCreate (upload) + K x LGBM_BoosterUpdateOneIter + LGBM_BoosterGetPredict, / K"},
         "gpu_launches": int(launches),
-        "roofline": {"bound": "hbm", "kernel": "k_hist (block-shared sub-histogram, 32-bit shared atomic pairs, DSMEM cluster reduce; global-atomic path for leaves < 256 rows)",
+        "roofline": {"bound": "hbm", "kernel": "k_hist (block-shared sub-histogram of 32 features, lane = feature, one byte load per (row, lane), "
+                                               "32-bit shared atomic pairs, DSMEM cluster reduce; global-atomic path for leaves < 256 rows)",
                      "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak if peak else None,
-                     "traffic": traffic, "peak_source": "MEASURED_PEAKS.json hbm_gbs (of measured)" if peaks else "fallback 6650 (of fallback)",
+                     "traffic": None, "peak_source": "MEASURED_PEAKS.json hbm_gbs (of measured)" if peaks else "fallback 6650 (of fallback)",
                      "launches": hist_launches, "leaf_histograms": int(hist_calls.value), "ms": hist_ms.value, "bytes": hist_bytes.value,
                      "algorithmic_bytes_per_launch": hist_bytes.value / max(1, hist_launches),
-                     "note": "achieved/traffic are per-launch averages over every histogram launch of %d iterations (one launch per "
-                             "round of tree growth, each building the histograms of up to 16 leaves; ~25 rounds per tree); the "
-                             "root launch alone runs at ~1 TB/s, see profiles/" % prof_iters},
+                     "note": "achieved is the average over every histogram launch of %d iterations (one launch per round of tree "
+                             "growth, each building the histograms of up to 16 leaves), CUDA events around the kernel alone; "
+                             "DRAM traffic per launch is in the ncu captures under profiles/, not measurable in the run" % prof_iters},
+        "phases_ms_per_iter": {"hist_plus_allreduce": phases[0] / prof_iters, "hist_kernel": phases[1] / prof_iters,
+                               "find_split_and_control": phases[2] / prof_iters, "partition": phases[4] / prof_iters,
+                               "rounds": phases[7] / prof_iters},
         "cpu_baseline": cpu,
-        "train_check": {"mean_score": float(np.mean(scores))},
+        "train_check": check,
     }
     emit(line)
     return 0

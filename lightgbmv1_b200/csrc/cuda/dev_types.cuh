@@ -54,7 +54,11 @@ struct DevLeaf {     // DataPartition range + LeafSplits + pool slot of one leaf
   int gcount;        // rows of this leaf over ALL ranks (== count on one GPU); what the split search calls num_data
   double sum_g, sum_h;  // LeafSplits::sum_gradients/sum_hessians (from the parent's SplitInfo)
   double output;        // LeafSplits::weight (leaf output before shrinkage)
-  i64 tot_g, tot_h;     // exact fixed-point totals of the rows histogrammed into this leaf's slot
+  int ogh;              // where this leaf's (gq, hq) pairs lie IN LEAF ORDER ("ordered gradients"): 0 / 1 = V.ogh[ogh] at
+                        // [begin, begin + count) (written by the partition that made the leaf: only the smaller child gets
+                        // them), 2 = V.gq itself (identity root: row i is position i), -1 = nowhere: gather V.gq by row
+  int pad0;
+  i64 reserved;
 };
 
 // Look-ahead growth.  The reference grows a tree best-first: split the open leaf with the largest gain, learn the
@@ -123,7 +127,8 @@ struct DevView {
   int pool_slots;            // histogram slots in the pool
   long long bits_stride;     // words of part_bits per item
   double2* mfb_fix;          // [num_leaves slots][num_features] FixHistogram'd most-frequent-bin entry, in double
-  const float2* gh;          // interleaved (gradient, hessian) of the current iteration, written by k_absmax
+  const int4* gq;            // [num_data] per-row fixed-point (gradient, hessian) of the current tree (pack_gh), written by k_quantise
+  int4* ogh[2];              // leaf-ordered copies of gq, ping-pong like `indices` (see DevLeaf::ogh)
   int* indices[2];
   HistEntry* pool;           // [num_leaves][total_bin]
   DevLeaf* leaves;

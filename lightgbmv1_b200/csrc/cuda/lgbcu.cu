@@ -108,7 +108,7 @@ struct LgbCuContext {
   std::vector<DevFeat> h_feats;
   int8_t* d_feat_used = nullptr;
   // per-row state
-  float2* d_gh = nullptr;
+  int4* d_gq = nullptr; int4* d_ogh[2] = {nullptr, nullptr};  // fixed-point (g, h) records: per row, and leaf-ordered ping-pong
   float *d_grad = nullptr, *d_hess = nullptr, *d_label = nullptr, *d_weight = nullptr;
   bool has_weight = false, has_label = false;
   double* d_score = nullptr;
@@ -170,7 +170,7 @@ struct LgbCuContext {
     V.bins = d_bins; V.feats = d_feats; V.feat_used = d_feat_used; V.splittable = d_splittable;
     V.parent_split = d_parent_split; V.mfb_fix = d_mfb_fix; V.spec = d_spec; V.expanded = d_expanded; V.pool_slots = pool_slots;
     V.bits_stride = bits_stride; V.part_sync_stride = part_sync_stride;
-    V.gh = d_gh; V.indices[0] = d_indices[0]; V.indices[1] = d_indices[1];
+    V.gq = d_gq; V.ogh[0] = d_ogh[0]; V.ogh[1] = d_ogh[1]; V.indices[0] = d_indices[0]; V.indices[1] = d_indices[1];
     V.pool = d_pool; V.leaves = d_leaves; V.best = d_best; V.feat_best = d_feat_best; V.feat_key = d_feat_key; V.leaf_key = d_leaf_key; V.ctl = d_ctl;
     V.records = d_records; V.part_sync = d_part_sync; V.bins_col = d_bins_col; V.col_stride = col_stride; V.part_bits = d_part_bits; V.p = params;
     V.data_parallel = (comm != nullptr || force_dp_counts) ? 1 : 0;
@@ -426,7 +426,7 @@ int lgbcu_destroy(LgbCuContext* c) {
   drop_graph(c);
   lgbcu_comm_destroy(c);
   free_valid_sets(c);
-  void* ptrs[] = {c->d_bins, c->d_feats, c->d_feat_used, c->d_grad, c->d_hess, c->d_gh, c->d_label, c->d_weight, c->d_score,
+  void* ptrs[] = {c->d_bins, c->d_feats, c->d_feat_used, c->d_grad, c->d_hess, c->d_gq, c->d_ogh[0], c->d_ogh[1], c->d_label, c->d_weight, c->d_score,
                   c->d_indices[0], c->d_indices[1], c->d_part_bits, c->d_part_sync, c->d_bins_col, c->d_query, c->d_label_gain,
                   c->d_inv_max_dcg, c->d_sigmoid_table, c->d_pool, c->d_splittable, c->d_leaves, c->d_best,
                   c->d_feat_best, c->d_ctl, c->d_records, c->d_leaf_value, c->d_export, c->d_tree_i32, c->d_tree_i8,
@@ -485,7 +485,9 @@ static int setup_dataset_common(LgbCuContext* c, int32_t num_data, int32_t num_f
   CU(cudaMemsetAsync(c->d_parent_split, 1, (size_t)LGB_KMAX * num_features, c->stream));
   CU(dev_alloc(&c->d_grad, (size_t)num_data));
   CU(dev_alloc(&c->d_hess, (size_t)num_data));
-  CU(dev_alloc(&c->d_gh, (size_t)num_data));
+  CU(dev_alloc(&c->d_gq, (size_t)num_data));
+  CU(dev_alloc(&c->d_ogh[0], (size_t)num_data));
+  CU(dev_alloc(&c->d_ogh[1], (size_t)num_data));
   CU(dev_alloc(&c->d_score, (size_t)num_data));
   CU(cudaMemsetAsync(c->d_score, 0, sizeof(double) * num_data, c->stream));
   CU(dev_alloc(&c->d_indices[0], (size_t)num_data));
@@ -819,9 +821,11 @@ int lgbcu_begin_tree(LgbCuContext* c, const int32_t* bag_indices, int32_t bag_co
   // only the root's slot: every later slot is zeroed by the partition launch that hands it out
   CU(cudaMemsetAsync(c->d_pool, 0, sizeof(HistEntry) * (size_t)c->total_bin, c->stream));
   LAUNCH(k_reset_ctl_max, 1, 1, 0, c->stream, c->d_ctl, c->root_count, c->N);
-  LAUNCH(k_absmax, grid_for(c, c->N, 256), 256, 0, c->stream, c->N, c->d_grad, c->d_hess, c->d_gh, c->d_ctl);
+  LAUNCH(k_absmax, grid_for(c, c->N, 256), 256, 0, c->stream, c->N, c->d_grad, c->d_hess, c->d_ctl);
   if (comm_allreduce_tree_setup(c)) return -1;
   LAUNCH(k_prepare_tree, 1, 256, 0, c->stream, c->view(), c->root_count, identity, c->lookahead);
+  LAUNCH(k_quantise, grid_for(c, c->root_count, 256), 256, 0, c->stream, c->N, c->d_grad, c->d_hess, c->d_ctl, c->d_gq,
+         identity ? nullptr : c->d_indices[0], c->root_count, c->d_ogh[0]);
   CU(cudaGetLastError());
   if (bag_indices || feature_used) CU(cudaStreamSynchronize(c->stream));  // caller may reuse its buffers
   c->tree_begun = true;
@@ -958,6 +962,7 @@ static int enqueue_round(LgbCuContext* c, int round, cudaEvent_t* ev) {
   const int K = c->lookahead;
   if (ev) CU(cudaEventRecord(ev[0], c->stream));
   if (launch_hist(c, -1)) return -1;
+  if (ev) CU(cudaEventRecord(ev[4], c->stream));  // end of the histogram kernel itself (the all-reduce follows)
   if (c->comm) {  // slots of a round are a function of (round, item): the collective is enqueued blind
     const int first = round == 0 ? 0 : 1 + (round - 1) * K, count = round == 0 ? 1 : K;
     NEED(first + count <= c->pool_slots, "lgbcu_train_tree: round %d needs histogram slots [%d, %d) but the pool has %d", round, first, first + count, c->pool_slots);
@@ -985,7 +990,7 @@ int lgbcu_train_tree(LgbCuContext* c, LgbCuSplitRecord* records, int32_t* num_sp
   int first_batch = 2 + ((L - 1) * 8 / 5 + K - 1) / K;
   if (first_batch > max_rounds) first_batch = max_rounds;
   int round = 0;
-  const int EV = 4;  // events per round: before hist, after hist (+ all-reduce), after find, after partition
+  const int EV = 5;  // events per round: before hist, after hist + all-reduce, after find, after partition; [4] = after hist alone
   if (prof && (int)c->ev.size() < EV * max_rounds) {
     const size_t old = c->ev.size();
     c->ev.resize(EV * max_rounds);
@@ -1039,8 +1044,10 @@ int lgbcu_train_tree(LgbCuContext* c, LgbCuSplitRecord* records, int32_t* num_sp
       for (int k = 0; k < 3; ++k) {
         float ms = 0; CU(cudaEventElapsedTime(&ms, c->ev[EV * r + k], c->ev[EV * r + k + 1]));
         c->loop_phase_ms[slot[k]] += ms;
-        if (k == 0) c->prof_hist_ms += ms;
       }
+      float hms = 0; CU(cudaEventElapsedTime(&hms, c->ev[EV * r], c->ev[EV * r + 4]));
+      c->prof_hist_ms += hms;               // the kernel alone: what the roofline figure is about
+      c->loop_phase_ms[1] += hms;           // [0] = histogram + all-reduce, [1] = histogram kernel alone
     }
     c->loop_phase_valid = true;
     if (const char* path = std::getenv("LGBCU_PROF_DUMP")) {  // per-round phase times (us), for offline analysis

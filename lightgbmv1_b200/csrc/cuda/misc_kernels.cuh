@@ -38,14 +38,10 @@ __global__ void k_grad_l2(int n, const double* __restrict__ score, const float* 
 }
 
 // max |g|, max |h| as float bit patterns (non-negative floats order like unsigned ints)
-// Also writes the interleaved (g, h) copy the histogram kernel gathers from: one 8-byte load per indexed row
-// instead of two 4-byte loads in two different sectors.
-__global__ void k_absmax(int n, const float* __restrict__ grad, const float* __restrict__ hess, float2* __restrict__ gh,
-                         DevCtl* ctl) {
+__global__ void k_absmax(int n, const float* __restrict__ grad, const float* __restrict__ hess, DevCtl* ctl) {
   unsigned mg = 0, mh = 0;
   for (int i = blockIdx.x * blockDim.x + threadIdx.x; i < n; i += gridDim.x * blockDim.x) {
     const float g = grad[i], h = hess[i];
-    gh[i] = make_float2(g, h);
     mg = max(mg, __float_as_uint(fabsf(g)));
     mh = max(mh, __float_as_uint(fabsf(h)));
   }
@@ -59,13 +55,15 @@ __global__ void k_absmax(int n, const float* __restrict__ grad, const float* __r
   }
 }
 
-// 2^k such that  max|v| * 2^k * rows < 2^62 : sums of `rows` fixed-point values cannot overflow an int64.
+// 2^k such that  max|v| * 2^k * rows < 2^62  (sums of `rows` fixed-point values cannot overflow an int64)  and
+// max|v| * 2^k < 2^46  (a row's value fits the 32 + 16 bit record the histogram kernel consumes, pack_gh).
 __device__ __forceinline__ int fixed_exponent(unsigned max_bits, long long rows) {
   const float m = __uint_as_float(max_bits);
   if (!(m > 0.f) || isinf(m) || isnan(m)) return 0;
   int e; frexpf(m, &e);          // m < 2^e
   int rb = 0; while ((1ll << rb) <= rows) ++rb;  // rows < 2^rb
   int k = 62 - e - rb;
+  if (k > 46 - e) k = 46 - e;
   if (k > 900) k = 900;
   if (k < -900) k = -900;
   return k;
@@ -91,8 +89,8 @@ __global__ void k_prepare_tree(DevView V, int root_count, int root_identity, int
     V.best[l] = none;
     { SplitKey k; k.gain = LGB_MIN_SCORE; k.real_feature = -1; k.pad = 0; V.leaf_key[l] = k; }
     DevLeaf z; z.begin = 0; z.count = 0; z.slot = l; z.depth = 0; z.buf = 0; z.gcount = 0;
-    z.sum_g = z.sum_h = z.output = 0; z.tot_g = z.tot_h = 0;
-    if (l == 0) { z.count = root_count; z.gcount = groot; }
+    z.sum_g = z.sum_h = z.output = 0; z.ogh = -1; z.pad0 = 0; z.reserved = 0;
+    if (l == 0) { z.count = root_count; z.gcount = groot; z.ogh = root_identity ? 2 : 0; }
     V.leaves[l] = z;
     V.expanded[l] = 0;
   }
@@ -110,6 +108,23 @@ __global__ void k_prepare_tree(DevView V, int root_count, int root_identity, int
     // BeforeFindBestSplit for the root: right child count is 0 (serial_tree_learner.h GetGlobalDataCountInLeaf)
     c->skip_find = (0 < V.p.min_data_in_leaf * 2 && groot < V.p.min_data_in_leaf * 2) ? 1 : 0;
     if (V.p.num_leaves < 2) c->done = 1;
+  }
+}
+
+// Per-row fixed-point (gradient, hessian) of the tree about to be grown; for a bagged root also its leaf-ordered copy
+// (root position p holds row idx[p]).  Runs after k_prepare_tree (the scales depend on max|g|, max|h| over all ranks).
+__global__ void k_quantise(int n, const float* __restrict__ grad, const float* __restrict__ hess, const DevCtl* __restrict__ ctl,
+                           int4* __restrict__ gq, const int* __restrict__ root_idx, int root_count, int4* __restrict__ root_ogh) {
+  const double sg = ctl->scale_g, sh = ctl->scale_h;
+  if (root_idx == nullptr) {
+    for (int i = blockIdx.x * blockDim.x + threadIdx.x; i < n; i += gridDim.x * blockDim.x)
+      gq[i] = pack_gh(__double2ll_rn((double)grad[i] * sg), __double2ll_rn((double)hess[i] * sh));
+  } else {
+    for (int p = blockIdx.x * blockDim.x + threadIdx.x; p < root_count; p += gridDim.x * blockDim.x) {
+      const int i = root_idx[p];
+      const int4 q = pack_gh(__double2ll_rn((double)grad[i] * sg), __double2ll_rn((double)hess[i] * sh));
+      gq[i] = q; root_ogh[p] = q;
+    }
   }
 }
 
@@ -131,7 +146,7 @@ __global__ void k_zero_slot(DevView V, int leaf) {
   HistEntry* a = V.pool + (size_t)V.leaves[leaf].slot * V.total_bin;
   HistEntry z; z.g = 0; z.h = 0;
   for (int i = blockIdx.x * blockDim.x + threadIdx.x; i < V.total_bin; i += gridDim.x * blockDim.x) a[i] = z;
-  if (blockIdx.x == 0 && threadIdx.x == 0) { V.leaves[leaf].tot_g = 0; V.leaves[leaf].tot_h = 0; }
+
 }
 
 // FixHistogram (src/io/dataset.cpp:1410-1428) for every feature of one slot, then conversion to hist_t doubles

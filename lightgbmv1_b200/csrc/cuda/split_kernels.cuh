@@ -500,9 +500,11 @@ __device__ void find_item(const DevView& V, ScanSmem& S, int f, int sel, const F
     const DevFeat F = V.feats[f];
     const DevLeaf Ls = T.Ls;
     int used = V.feat_used[f] != 0;
-    // a feature with no valid threshold in the parent is skipped in both children (serial_tree_learner.cpp:319-326);
-    // k_partition snapshotted the parent's flags, so sibling blocks cannot race on them
-    if (T.has_larger && T.parent_split) used = used && T.parent_split[f] != 0;
+    // a feature with no valid threshold in the parent is skipped in both children (SerialTreeLearner::FindBestSplits,
+    // serial_tree_learner.cpp:319-326); k_partition snapshotted the parent's flags, so sibling blocks cannot race on
+    // them.  The data-parallel learner overrides FindBestSplits without that mask (data_parallel_tree_learner.cpp:
+    // 155-173: every by-tree feature is histogrammed and scanned for every leaf), so there the flags are not applied.
+    if (T.has_larger && T.parent_split && !V.data_parallel) used = used && T.parent_split[f] != 0;
     const int nt = F.num_bin - F.offset;
     const double inv_g = c->inv_g, inv_h = c->inv_h;
     HistEntry* hs = V.pool + (size_t)Ls.slot * V.total_bin + F.hist_base;  // smaller leaf, slot 0 of the group

@@ -49,9 +49,8 @@ GBDT::GBDT(const Dataset* train, const Config& config)
   Check(lgbcu_create(dev, &ctx_));
   st.tick("lgbcu_create");
   // the communicator comes first: the objective's Init sums class counts over the machines
-  if (Net().active && Net().num_machines > 1 && config_.tree_learner == "data") {
-    Check(lgbcu_comm_init(ctx_, Net().unique_id, Net().rank, Net().num_machines));
-  }
+  data_parallel_ = Net().active && Net().num_machines > 1 && config_.tree_learner == "data";
+  if (data_parallel_) Check(lgbcu_comm_init(ctx_, Net().unique_id, Net().rank, Net().num_machines));
   if (objective_) {
     LgbCuContext* ctx = ctx_;
     objective_->Init(train_->metadata(), N, [ctx](double* v, int n) { Check(lgbcu_comm_allreduce_sum_f64(ctx, v, n)); });
@@ -172,7 +171,7 @@ bool GBDT::TrainOneIter(const float* grad, const float* hess) {
     // BoostFromAverage (gbdt.cpp:312-335)
     if (models_.empty() && !has_init_score_ && config_.boost_from_average) {
       double s = objective_->BoostFromScore();
-      if (Net().active && Net().num_machines > 1) {  // Network::GlobalSyncUpByMean
+      if (data_parallel_) {  // Network::GlobalSyncUpByMean
         Check(lgbcu_comm_allreduce_sum_f64(ctx_, &s, 1));
         s /= Net().num_machines;
       }

@@ -68,6 +68,7 @@ class GBDT {
   int iter_ = 0;
   double shrinkage_rate_;
   bool has_init_score_ = false;
+  bool data_parallel_ = false;  // this booster trains over the NCCL communicator (tree_learner=data, num_machines > 1)
   bool class_need_train_ = true;
   // bagging (gbdt.cpp:209-243, 739-797)
   std::vector<data_size_t> bag_indices_;  // in-bag (ascending) then out-of-bag (ascending)

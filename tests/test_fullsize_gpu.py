@@ -62,8 +62,8 @@ def test_full_size_properties(n, F, leaves, name):
     sg, sh, cnt = L.get_leaf_sums(0)
     assert cnt == n
     G = float(np.sum(g.astype(np.float64))); Hs = float(np.sum(h.astype(np.float64)))
-    assert abs(sg - G) <= 1e-9 * float(np.sum(np.abs(g.astype(np.float64))))
-    assert abs(sh - Hs) <= 1e-9 * Hs
+    assert abs(sg - G) <= H.VALUE_RTOL * float(np.sum(np.abs(g.astype(np.float64))))
+    assert abs(sh - Hs) <= H.VALUE_RTOL * Hs
     bases, total = H.hist_bases(metas)
     for f in (0, 6, 8, F - 1):
         ns = H.nslots(metas[f])
@@ -71,8 +71,8 @@ def test_full_size_properties(n, F, leaves, name):
         # slot 0 (most-frequent bin rows) is duplicated at slot 1+mfb for mfb > 0 features: count it once
         dup = 1 + metas[f][1] if metas[f][1] > 0 else None
         tg = hg.sum() - (hg[dup] if dup is not None else 0.0); th = hh.sum() - (hh[dup] if dup is not None else 0.0)
-        assert abs(tg - sg) <= 1e-9 * float(np.sum(np.abs(g.astype(np.float64))))
-        assert abs(th - sh) <= 1e-9 * sh
+        assert abs(tg - sg) <= H.VALUE_RTOL * float(np.sum(np.abs(g.astype(np.float64))))
+        assert abs(th - sh) <= H.VALUE_RTOL * sh
     if name == "higgs":
         L.set_hist_mode(N.HIST_GLOBAL_ATOMIC)
         L.begin_tree(); L.hist_build(0)

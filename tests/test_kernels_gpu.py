@@ -74,8 +74,8 @@ def test_root_histogram(orc, mode, n, F):
     assert _compare_hist(metas, got, want, g, h) <= H.HIST_RTOL
     sg, sh, cnt = L.get_leaf_sums(0)
     assert cnt == n
-    assert abs(sg - float(np.sum(g.astype(np.float64)))) <= 1e-9 * float(np.sum(np.abs(g.astype(np.float64))) + 1e-30)
-    assert abs(sh - float(np.sum(h.astype(np.float64)))) <= 1e-9 * float(np.sum(h.astype(np.float64)))
+    assert abs(sg - float(np.sum(g.astype(np.float64)))) <= H.VALUE_RTOL * float(np.sum(np.abs(g.astype(np.float64))) + 1e-30)
+    assert abs(sh - float(np.sum(h.astype(np.float64)))) <= H.VALUE_RTOL * float(np.sum(h.astype(np.float64)))
     L.close()
 
 
@@ -178,9 +178,9 @@ def test_find_best_split_root(orc, pi, kinds):
     if want.feature >= 0 and np.isfinite(want.gain):
         for a, b in [(got.gain, want.gain), (got.left_output, want.left_output), (got.right_output, want.right_output),
                      (got.left_sum_hessian, want.left_sum_hessian), (got.right_sum_hessian, want.right_sum_hessian)]:
-            assert abs(a - b) <= 1e-9 * max(abs(b), 1e-12) + 1e-12
+            assert abs(a - b) <= H.VALUE_RTOL * max(abs(b), 1e-12) + 1e-12
         for a, b in [(got.left_sum_gradient, want.left_sum_gradient), (got.right_sum_gradient, want.right_sum_gradient)]:
-            assert abs(a - b) <= 1e-9 * float(np.sum(np.abs(g)))
+            assert abs(a - b) <= H.VALUE_RTOL * float(np.sum(np.abs(g)))
     L.close()
 
 
@@ -266,7 +266,7 @@ def _orc_train(orc, bins, metas, params, g, h, bag=None, used=None):
 
 def _check_tree(L, got, want, leaf_of_row, n, bag=None):
     """Split records must be identical.  The one tolerated deviation (north_star: "except on gain near-ties") is
-    a pair of candidates whose gains agree to 1e-9 relative: then the records may differ from that split on, and
+    a pair of candidates whose gains agree to H.VALUE_RTOL relative: then the records may differ from that split on, and
     only the GPU tree's own consistency is checked past it."""
     k = 0
     while k < min(len(got), len(want)) and H.records_to_tuples([got[k]]) == H.records_to_tuples([want[k]]):
@@ -275,13 +275,13 @@ def _check_tree(L, got, want, leaf_of_row, n, bag=None):
         assert abs(a.gain - b.gain) <= 1e-6 * max(abs(b.gain), 1e-6)
         for x, y in [(a.left_output, b.left_output), (a.right_output, b.right_output),
                      (a.left_sum_hessian, b.left_sum_hessian), (a.right_sum_hessian, b.right_sum_hessian)]:
-            assert abs(x - y) <= 1e-9 * max(abs(y), 1e-9)
+            assert abs(x - y) <= H.VALUE_RTOL * max(abs(y), 1e-9)
         k += 1
     exact = k == len(got) == len(want)
     if not exact:
         assert k < len(got) and k < len(want), "one tree stopped early"
         a, b = got[k], want[k]
-        assert abs(a.gain - b.gain) <= 1e-9 * max(abs(b.gain), 1e-9), \
+        assert abs(a.gain - b.gain) <= H.VALUE_RTOL * max(abs(b.gain), 1e-9), \
             f"split {k} differs and is not a near-tie: {H.records_to_tuples([a])} vs {H.records_to_tuples([b])}"
     # leaf assignment: every bagged row in exactly one leaf, ascending inside a leaf (stable partition);
     # bit-exact against the oracle when the trees are identical

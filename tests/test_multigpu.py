@@ -1,7 +1,14 @@
-"""tree_learner=data over NCCL: (gpu, needs >= 2 GPUs) the 2-rank model must equal the 1-rank model grown with the
-same bin mappers and the data-parallel count semantics -- exact, because the histogram all-reduce is an integer sum.
-(cpu, gloo, world_size 2) the host-side shard plumbing: shards built against a common reference dataset carry the
-same bin mappers and together hold exactly the bins of the unsharded matrix."""
+"""tree_learner=data (A11).  The oracle is the reference's OWN data-parallel learner: 2 machines over localhost sockets,
+contiguous row shards binned against a common reference dataset (tests/golden/make_dp_golden.py wrote rank 0's model
+to tests/golden/dp_reference_2rank_model.txt).  The shards are sorted by a feature, so class balance and feature ranges
+differ between the machines and some leaves have no rows on one of them.
+  (gpu, 1 GPU)      one rank with the data-parallel count semantics (LGBCU_FORCE_DP_COUNTS) on the unsharded matrix,
+                    same bin mappers, must reproduce the reference's 2-machine model;
+  (gpu, >= 2 GPUs)  the 2-rank NCCL run must reproduce it too -- and equal the 1-rank run bit for bit (the histogram
+                    all-reduce is an integer sum); with is_unbalance the label weights come from the class counts of
+                    ALL ranks (binary_objective.hpp:72-75);
+  (cpu, gloo, world_size 2) the host-side shard plumbing: shards built against a common reference dataset carry the
+                    same bin mappers and together hold exactly the bins of the unsharded matrix."""
 import ctypes as C
 import os
 import subprocess
@@ -14,23 +21,54 @@ import capi
 import helpers as H
 from lightgbmv1_b200 import _native as N
 
+GOLDEN = os.path.join(H.ROOT, "tests", "golden", "dp_reference_2rank_model.txt")
+SCRIPT = os.path.join(H.ROOT, "tools", "run_dp.py")
+
+
+def _torchrun(nproc, port, out, extra=""):
+    cmd = [sys.executable, "-m", "torch.distributed.run", "--nnodes=1", f"--nproc-per-node={nproc}",
+           "--master-addr", "127.0.0.1", "--master-port", str(port), SCRIPT, "--out", out]
+    if extra:
+        cmd += ["--extra", extra]
+    subprocess.check_call(cmd, env=dict(os.environ), timeout=900)
+
+
+def _assert_same(a, b, what):
+    same, n, first = capi.compare_models(a, b, rtol_value=H.VALUE_RTOL)
+    assert n > 0 and same == n, f"{what}: {same}/{n} trees identical; first mismatch: {first}"
+
 
 @pytest.mark.gpu
-def test_two_rank_model_equals_one_rank_model(tmp_path):
+def test_one_rank_with_dp_counts_reproduces_the_reference_two_machine_model(tmp_path):
+    one = str(tmp_path / "one.txt")
+    subprocess.check_call([sys.executable, SCRIPT, "--out", one], env=dict(os.environ, LGBCU_FORCE_DP_COUNTS="1"), timeout=600)
+    _assert_same(open(GOLDEN).read(), open(one).read(), "reference 2-machine socket run vs 1 rank with data-parallel counts")
+
+
+@pytest.mark.gpu
+def test_two_rank_model_equals_reference_two_machine_model_and_one_rank_model(tmp_path):
     if N.device_count() < 2:
         pytest.skip("needs 2 GPUs")
-    env = dict(os.environ)
     one, two = str(tmp_path / "one.txt"), str(tmp_path / "two.txt")
-    script = os.path.join(H.ROOT, "tools", "run_dp.py")
-    env1 = dict(env, LGBCU_FORCE_DP_COUNTS="1")
-    subprocess.check_call([sys.executable, script, "--out", one], env=env1, timeout=600)
-    subprocess.check_call([sys.executable, "-m", "torch.distributed.run", "--nnodes=1", "--nproc-per-node=2",
-                           "--master-addr", "127.0.0.1", "--master-port", "29511", script, "--out", two],
-                          env=env, timeout=900)
+    subprocess.check_call([sys.executable, SCRIPT, "--out", one], env=dict(os.environ, LGBCU_FORCE_DP_COUNTS="1"), timeout=600)
+    _torchrun(2, 29511, two)
     a, b = open(one).read(), open(two).read()
+    _assert_same(open(GOLDEN).read(), b, "reference 2-machine socket run vs 2-rank NCCL run")
     same, n, first = capi.compare_models(a, b, rtol_value=0.0)
-    assert same == n == 5, (same, n, first)
+    assert same == n, (same, n, first)
     assert a.split("parameters:")[0] == b.split("parameters:")[0]
+
+
+@pytest.mark.gpu
+def test_two_rank_is_unbalance_uses_global_class_counts(tmp_path):
+    if N.device_count() < 2:
+        pytest.skip("needs 2 GPUs")
+    one, two = str(tmp_path / "one.txt"), str(tmp_path / "two.txt")
+    subprocess.check_call([sys.executable, SCRIPT, "--out", one, "--extra", "is_unbalance=true"],
+                          env=dict(os.environ, LGBCU_FORCE_DP_COUNTS="1"), timeout=600)
+    _torchrun(2, 29512, two, extra="is_unbalance=true")
+    same, n, first = capi.compare_models(open(one).read(), open(two).read(), rtol_value=0.0)
+    assert same == n, (same, n, first)
 
 
 def _gloo_worker(rank, world, port, q):

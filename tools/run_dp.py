@@ -1,29 +1,27 @@
-"""Data-parallel training driver (one process per GPU; launched with torchrun).  Trains `iters` iterations on a
-row shard with tree_learner=data over NCCL and writes the model text of rank 0 to --out.  With WORLD_SIZE=1 it
-trains on the full matrix (single GPU) using the SAME bin mappers, so the two runs can be compared."""
+"""Data-parallel training driver (one process per GPU; launched with torchrun).  Trains the case of
+tests/golden/make_dp_golden.py -- the same matrix, shards, common reference dataset, parameters and iteration count
+as the reference's own 2-machine socket run -- with tree_learner=data over NCCL and writes rank 0's model text to
+--out.  With WORLD_SIZE=1 it trains on the full matrix (single GPU) using the SAME bin mappers; with
+LGBCU_FORCE_DP_COUNTS=1 that run uses the data-parallel count semantics and must give the same model."""
 import argparse, ctypes as C, os, sys
 ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
-sys.path.insert(0, ROOT); sys.path.insert(0, os.path.join(ROOT, "tests"))
+sys.path.insert(0, ROOT); sys.path.insert(0, os.path.join(ROOT, "tests")); sys.path.insert(0, os.path.join(ROOT, "tests", "golden"))
 import numpy as np
 import capi
+import make_dp_golden as G
 
 ap = argparse.ArgumentParser()
-ap.add_argument("--rows", type=int, default=200_000)
-ap.add_argument("--iters", type=int, default=5)
-ap.add_argument("--leaves", type=int, default=31)
 ap.add_argument("--out", default="")
+ap.add_argument("--extra", default="", help="extra parameters, e.g. is_unbalance=true")
+ap.add_argument("--iters", type=int, default=G.ITERS)
 args = ap.parse_args()
 rank = int(os.environ.get("RANK", "0")); world = int(os.environ.get("WORLD_SIZE", "1")); local = int(os.environ.get("LOCAL_RANK", "0"))
 
-rng = np.random.default_rng(0)
-n, F = args.rows, 28
-X = rng.standard_normal((n, F)).astype(np.float32)
-X[:, 21:25] = np.maximum(0, X[:, 21:25])
-w = np.random.default_rng(1).standard_normal(F)
-y = ((X @ w + 0.5 * X[:, 0] * X[:, 1] + rng.standard_normal(n)) > 0).astype(np.float32)
+X, y, ref_rows = G.dp_case()
+n = len(y)
 ours = capi.ours(); lib = ours.lib
-base = f"objective=binary num_leaves={args.leaves} learning_rate=0.1 min_data_in_leaf=20 boost_from_average=false verbosity=-1"
-ref_ds = ours.dataset_from_mat(X[:50_000], base)
+base = G.BASE + (" " + args.extra if args.extra else "")
+ref_ds = ours.dataset_from_mat(np.ascontiguousarray(X[ref_rows]), base)
 if world > 1:
     import torch, torch.distributed as dist
     torch.cuda.set_device(local)
@@ -56,4 +54,7 @@ if world > 1:
     dist.all_gather(lst, tt)
     assert all(int(x) == h for x in lst), "ranks disagree on the model"
     dist.barrier()
+    ours.booster_free(b)
+    ours.check(lib.LGBM_NetworkFree())
+    dist.destroy_process_group()
 print(f"rank {rank}/{world} done", flush=True)
