@@ -54,10 +54,7 @@ struct DevLeaf {     // DataPartition range + LeafSplits + pool slot of one leaf
   int gcount;        // rows of this leaf over ALL ranks (== count on one GPU); what the split search calls num_data
   double sum_g, sum_h;  // LeafSplits::sum_gradients/sum_hessians (from the parent's SplitInfo)
   double output;        // LeafSplits::weight (leaf output before shrinkage)
-  int ogh;              // where this leaf's (gq, hq) pairs lie IN LEAF ORDER ("ordered gradients"): 0 / 1 = V.ogh[ogh] at
-                        // [begin, begin + count) (written by the partition that made the leaf: only the smaller child gets
-                        // them), 2 = V.gq itself (identity root: row i is position i), -1 = nowhere: gather V.gq by row
-  int pad0;
+  int pad0, pad1;
   i64 reserved;
 };
 
@@ -68,7 +65,7 @@ struct DevLeaf {     // DataPartition range + LeafSplits + pool slot of one leaf
 // the largest gains side by side (the kernels of a round are latency bound, so K leaves cost about as much as one),
 // then commits, in the reference's order, every leaf whose turn has come and whose children are ready.  An expansion
 // is only wasted if the leaf budget runs out before the leaf's turn.
-#define LGB_KMAX 16
+#define LGB_KMAX 32
 
 struct DevSpec {     // an expanded leaf that is not committed yet: what Split + two FindBestThreshold runs produced
   DevLeaf child[2];  // [0] = left (keeps the parent's leaf id when committed), [1] = right (gets the next free id)
@@ -115,7 +112,10 @@ struct DevParams {   // LgbCuTreeParams + derived switches
 struct DevView {
   int num_data, num_features, row_stride, total_bin, num_tiles16;
   int data_parallel;         // 1: histograms are all-reduced across ranks, leaf counts are the global estimates
-  const uint8_t* bins;
+  int rec_off;               // byte offset of the (g, h) record inside a row of `bins`
+  uint8_t* bins;             // [num_data][row_stride]: the row's stored bins, then (at rec_off) its 16-byte fixed-point
+                             // (g, h) record of the current tree (pack_gh, written by k_quantise): one 64-byte DRAM burst
+                             // serves both when the histogram kernel gathers a row of an indexed leaf
   const uint8_t* bins_col;   // column-major copy [F][col_stride]: the partition of a large leaf reads one feature of
   long long col_stride;      // (nearly) consecutive rows -- 32 rows per sector instead of one
   const DevFeat* feats;
@@ -127,8 +127,7 @@ struct DevView {
   int pool_slots;            // histogram slots in the pool
   long long bits_stride;     // words of part_bits per item
   double2* mfb_fix;          // [num_leaves slots][num_features] FixHistogram'd most-frequent-bin entry, in double
-  const int4* gq;            // [num_data] per-row fixed-point (gradient, hessian) of the current tree (pack_gh), written by k_quantise
-  int4* ogh[2];              // leaf-ordered copies of gq, ping-pong like `indices` (see DevLeaf::ogh)
+  const int4* gq;            // [num_data] contiguous copy of the records: what the full-data root pass streams
   int* indices[2];
   HistEntry* pool;           // [num_leaves][total_bin]
   DevLeaf* leaves;

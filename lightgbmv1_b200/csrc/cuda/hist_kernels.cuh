@@ -22,8 +22,9 @@
 //                    Each wrap is seen by exactly the add that caused it and addition commutes, so (hi, lo) after
 //                    the block barrier is the exact 64-bit sum whatever the interleaving.
 //                    Feeding the lanes: a warp stages 32 rows at a time -- lane j loads row index j of the batch
-//                    (coalesced) and its fixed-point (g, h) record (coalesced from the leaf-ordered copy the partition
-//                    wrote, "ordered gradients"; gathered by row only for leaves that have none) into shared memory;
+//                    (coalesced) and that row's fixed-point (g, h) record (it lies in the row's own slot of the bin
+//                    matrix, so the 64-byte DRAM burst that brings the bins brings it too; the full-data root pass
+//                    streams a contiguous copy instead) into shared memory;
 //                    every lane then reads one 16-byte broadcast per row (row offset, g low, h low, packed high
 //                    words) and fetches ITS OWN bin of that row straight from the row-major matrix (32 lanes x 1 byte =
 //                    the row's 32-byte sector, one L1 wavefront, 16 loads in flight per warp): no transposition
@@ -67,11 +68,9 @@ __device__ __forceinline__ int4 pack_gh(i64 g, i64 h) {
 __device__ __forceinline__ i64 unpack_g(const int4& r) { return ((i64)(short)(r.z & 0xffff) << 32) | (unsigned)r.x; }
 __device__ __forceinline__ i64 unpack_h(const int4& r) { return ((i64)(r.z >> 16) << 32) | (unsigned)r.y; }
 
-// the leaf's (gq, hq) pairs in leaf order, or nullptr if it has none (DevLeaf::ogh)
-__device__ __forceinline__ const int4* leaf_ordered_gh(const DevView& V, const DevLeaf& L) {
-  if (L.ogh == 2) return V.gq;
-  if (L.ogh == 0 || L.ogh == 1) return V.ogh[L.ogh] + L.begin;
-  return nullptr;
+// a row's record, from the row's own slot in the bin matrix (the same 64-byte burst as its bins)
+__device__ __forceinline__ int4 row_record(const DevView& V, int row) {
+  return *reinterpret_cast<const int4*>(V.bins + (size_t)row * V.row_stride + V.rec_off);
 }
 
 __device__ void hist_global_path(const DevView& V, const DevLeaf& L, bool identity, int bid, int nblocks) {
@@ -84,7 +83,7 @@ __device__ void hist_global_path(const DevView& V, const DevLeaf& L, bool identi
     const int ck = (int)(p - (long long)pos * nchunk);
     const int row = identity ? pos : idx[pos];
     const uint4 q = *reinterpret_cast<const uint4*>(V.bins + (size_t)row * V.row_stride + ck * 16);
-    const int4 gh = V.gq[row];
+    const int4 gh = row_record(V, row);
     const i64 gq = unpack_g(gh), hq = unpack_h(gh);
     const unsigned w[4] = {q.x, q.y, q.z, q.w};
 #pragma unroll
@@ -153,7 +152,6 @@ __device__ void hist_shared_path(const DevView& V, const DevLeaf& L, bool identi
   int per_block = (L.count + PG * HIST_CLUSTER - 1) / (PG * HIST_CLUSTER);
   per_block = (per_block + 31) / 32 * 32;
   const int* idx = V.indices[L.buf] + L.begin;
-  const int4* ordered = leaf_ordered_gh(V, L);
   HistEntry* out = V.pool + (size_t)L.slot * V.total_bin;
   const unsigned stride16 = (unsigned)V.row_stride / 16u;  // row offsets travel as 32-bit counts of 16 bytes (64 GB)
 #ifdef LGBCU_STAGE_TIMERS
@@ -175,7 +173,7 @@ __device__ void hist_shared_path(const DevView& V, const DevLeaf& L, bool identi
       const int pos = base + lane;
       if (pos < b1) {
         const int row = identity ? pos : idx[pos];
-        const int4 r = ordered ? ordered[pos] : V.gq[row];
+        const int4 r = identity ? V.gq[pos] : row_record(V, row);
         nst = make_int4((int)((unsigned)row * stride16), r.x, r.y, r.z);
       }
     }
@@ -195,7 +193,7 @@ __device__ void hist_shared_path(const DevView& V, const DevLeaf& L, bool identi
         const int pos1 = base + step + lane;
         if (pos1 < b1) {
           const int row = identity ? pos1 : idx[pos1];
-          const int4 r = ordered ? ordered[pos1] : V.gq[row];
+          const int4 r = identity ? V.gq[pos1] : row_record(V, row);
           nst = make_int4((int)((unsigned)row * stride16), r.x, r.y, r.z);
         }
       }

@@ -108,7 +108,8 @@ struct LgbCuContext {
   std::vector<DevFeat> h_feats;
   int8_t* d_feat_used = nullptr;
   // per-row state
-  int4* d_gq = nullptr; int4* d_ogh[2] = {nullptr, nullptr};  // fixed-point (g, h) records: per row, and leaf-ordered ping-pong
+  int4* d_gq = nullptr;  // fixed-point (g, h) records of the current tree, contiguous (the rows of d_bins hold a copy)
+  int rec_off = 0;
   float *d_grad = nullptr, *d_hess = nullptr, *d_label = nullptr, *d_weight = nullptr;
   bool has_weight = false, has_label = false;
   double* d_score = nullptr;
@@ -170,7 +171,7 @@ struct LgbCuContext {
     V.bins = d_bins; V.feats = d_feats; V.feat_used = d_feat_used; V.splittable = d_splittable;
     V.parent_split = d_parent_split; V.mfb_fix = d_mfb_fix; V.spec = d_spec; V.expanded = d_expanded; V.pool_slots = pool_slots;
     V.bits_stride = bits_stride; V.part_sync_stride = part_sync_stride;
-    V.gq = d_gq; V.ogh[0] = d_ogh[0]; V.ogh[1] = d_ogh[1]; V.indices[0] = d_indices[0]; V.indices[1] = d_indices[1];
+    V.gq = d_gq; V.rec_off = rec_off; V.indices[0] = d_indices[0]; V.indices[1] = d_indices[1];
     V.pool = d_pool; V.leaves = d_leaves; V.best = d_best; V.feat_best = d_feat_best; V.feat_key = d_feat_key; V.leaf_key = d_leaf_key; V.ctl = d_ctl;
     V.records = d_records; V.part_sync = d_part_sync; V.bins_col = d_bins_col; V.col_stride = col_stride; V.part_bits = d_part_bits; V.p = params;
     V.data_parallel = (comm != nullptr || force_dp_counts) ? 1 : 0;
@@ -426,7 +427,7 @@ int lgbcu_destroy(LgbCuContext* c) {
   drop_graph(c);
   lgbcu_comm_destroy(c);
   free_valid_sets(c);
-  void* ptrs[] = {c->d_bins, c->d_feats, c->d_feat_used, c->d_grad, c->d_hess, c->d_gq, c->d_ogh[0], c->d_ogh[1], c->d_label, c->d_weight, c->d_score,
+  void* ptrs[] = {c->d_bins, c->d_feats, c->d_feat_used, c->d_grad, c->d_hess, c->d_gq, c->d_label, c->d_weight, c->d_score,
                   c->d_indices[0], c->d_indices[1], c->d_part_bits, c->d_part_sync, c->d_bins_col, c->d_query, c->d_label_gain,
                   c->d_inv_max_dcg, c->d_sigmoid_table, c->d_pool, c->d_splittable, c->d_leaves, c->d_best,
                   c->d_feat_best, c->d_ctl, c->d_records, c->d_leaf_value, c->d_export, c->d_tree_i32, c->d_tree_i8,
@@ -455,8 +456,11 @@ static int setup_dataset_common(LgbCuContext* c, int32_t num_data, int32_t num_f
   NEED(num_features < (1 << KEY_FEAT_BITS), "lgbcu_set_dataset: %d features exceed the supported %d", num_features, (1 << KEY_FEAT_BITS) - 1);
   CU(cudaSetDevice(c->device));
   c->N = num_data; c->F = num_features;
-  c->stride = (num_features + 15) & ~15;
-  c->ntiles16 = c->stride / 16;
+  // a row = its stored bins (padded to 16 bytes), then the 16-byte (g, h) record of the current tree; rows are whole
+  // 32-byte sectors and at least one 64-byte DRAM burst, so that gathering a row never straddles more than it must
+  c->rec_off = (num_features + 15) & ~15;
+  c->ntiles16 = c->rec_off / 16;
+  c->stride = std::max(64, (c->rec_off + 16 + 31) & ~31);
   c->h_feats.resize(num_features);
   int base = 0;
   for (int f = 0; f < num_features; ++f) {
@@ -486,8 +490,6 @@ static int setup_dataset_common(LgbCuContext* c, int32_t num_data, int32_t num_f
   CU(dev_alloc(&c->d_grad, (size_t)num_data));
   CU(dev_alloc(&c->d_hess, (size_t)num_data));
   CU(dev_alloc(&c->d_gq, (size_t)num_data));
-  CU(dev_alloc(&c->d_ogh[0], (size_t)num_data));
-  CU(dev_alloc(&c->d_ogh[1], (size_t)num_data));
   CU(dev_alloc(&c->d_score, (size_t)num_data));
   CU(cudaMemsetAsync(c->d_score, 0, sizeof(double) * num_data, c->stream));
   CU(dev_alloc(&c->d_indices[0], (size_t)num_data));
@@ -510,9 +512,7 @@ int lgbcu_set_dataset(LgbCuContext* c, int32_t num_data, int32_t num_features, c
                       const LgbCuFeatureMeta* meta) {
   NEED(bins, "lgbcu_set_dataset: bins is NULL");
   if (setup_dataset_common(c, num_data, num_features, meta)) return -1;
-  if (c->stride == num_features) {
-    CU(cudaMemcpyAsync(c->d_bins, bins, (size_t)num_data * num_features, cudaMemcpyHostToDevice, c->stream));
-  } else {
+  {
     // one contiguous H2D copy, then pad rows to the 16-byte stride on the device (a strided 2-D copy of 28-byte rows
     // crawls: one DMA descriptor per row)
     uint8_t* packed = nullptr;
@@ -825,7 +825,7 @@ int lgbcu_begin_tree(LgbCuContext* c, const int32_t* bag_indices, int32_t bag_co
   if (comm_allreduce_tree_setup(c)) return -1;
   LAUNCH(k_prepare_tree, 1, 256, 0, c->stream, c->view(), c->root_count, identity, c->lookahead);
   LAUNCH(k_quantise, grid_for(c, c->root_count, 256), 256, 0, c->stream, c->N, c->d_grad, c->d_hess, c->d_ctl, c->d_gq,
-         identity ? nullptr : c->d_indices[0], c->root_count, c->d_ogh[0]);
+         c->d_bins, c->stride, c->rec_off, identity ? nullptr : c->d_indices[0], c->root_count);
   CU(cudaGetLastError());
   if (bag_indices || feature_used) CU(cudaStreamSynchronize(c->stream));  // caller may reuse its buffers
   c->tree_begun = true;

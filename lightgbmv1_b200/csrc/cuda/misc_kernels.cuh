@@ -89,8 +89,8 @@ __global__ void k_prepare_tree(DevView V, int root_count, int root_identity, int
     V.best[l] = none;
     { SplitKey k; k.gain = LGB_MIN_SCORE; k.real_feature = -1; k.pad = 0; V.leaf_key[l] = k; }
     DevLeaf z; z.begin = 0; z.count = 0; z.slot = l; z.depth = 0; z.buf = 0; z.gcount = 0;
-    z.sum_g = z.sum_h = z.output = 0; z.ogh = -1; z.pad0 = 0; z.reserved = 0;
-    if (l == 0) { z.count = root_count; z.gcount = groot; z.ogh = root_identity ? 2 : 0; }
+    z.sum_g = z.sum_h = z.output = 0; z.pad0 = z.pad1 = 0; z.reserved = 0;
+    if (l == 0) { z.count = root_count; z.gcount = groot; }
     V.leaves[l] = z;
     V.expanded[l] = 0;
   }
@@ -111,20 +111,20 @@ __global__ void k_prepare_tree(DevView V, int root_count, int root_identity, int
   }
 }
 
-// Per-row fixed-point (gradient, hessian) of the tree about to be grown; for a bagged root also its leaf-ordered copy
-// (root position p holds row idx[p]).  Runs after k_prepare_tree (the scales depend on max|g|, max|h| over all ranks).
+// Per-row fixed-point (gradient, hessian) record of the tree about to be grown (pack_gh), written twice: into the
+// row's slot of the bin matrix (what indexed histogram passes gather, together with the bins, in one DRAM burst) and
+// into the contiguous array the full-data root pass streams.  Runs after k_prepare_tree (the scales depend on
+// max|g|, max|h| over all ranks).  root_idx != nullptr: only the bagged rows.
 __global__ void k_quantise(int n, const float* __restrict__ grad, const float* __restrict__ hess, const DevCtl* __restrict__ ctl,
-                           int4* __restrict__ gq, const int* __restrict__ root_idx, int root_count, int4* __restrict__ root_ogh) {
+                           int4* __restrict__ gq, uint8_t* __restrict__ bins, int row_stride, int rec_off,
+                           const int* __restrict__ root_idx, int root_count) {
   const double sg = ctl->scale_g, sh = ctl->scale_h;
-  if (root_idx == nullptr) {
-    for (int i = blockIdx.x * blockDim.x + threadIdx.x; i < n; i += gridDim.x * blockDim.x)
-      gq[i] = pack_gh(__double2ll_rn((double)grad[i] * sg), __double2ll_rn((double)hess[i] * sh));
-  } else {
-    for (int p = blockIdx.x * blockDim.x + threadIdx.x; p < root_count; p += gridDim.x * blockDim.x) {
-      const int i = root_idx[p];
-      const int4 q = pack_gh(__double2ll_rn((double)grad[i] * sg), __double2ll_rn((double)hess[i] * sh));
-      gq[i] = q; root_ogh[p] = q;
-    }
+  const int count = root_idx ? root_count : n;
+  for (int p = blockIdx.x * blockDim.x + threadIdx.x; p < count; p += gridDim.x * blockDim.x) {
+    const int i = root_idx ? root_idx[p] : p;
+    const int4 q = pack_gh(__double2ll_rn((double)grad[i] * sg), __double2ll_rn((double)hess[i] * sh));
+    gq[i] = q;
+    *reinterpret_cast<int4*>(bins + (size_t)i * row_stride + rec_off) = q;
   }
 }
 

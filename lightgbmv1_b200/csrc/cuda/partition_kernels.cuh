@@ -70,7 +70,6 @@ __device__ void part_control_stepwise(const DevView& V, int leaf, const DevLeaf&
   DevLeaf A = L, B = L;  // A = left child (keeps the id), B = right child (new id R)
   A.count = left_cnt; A.buf = L.buf ^ 1; A.depth = L.depth + 1; A.gcount = left_cnt;
   B.begin = L.begin + left_cnt; B.count = right_cnt; B.buf = L.buf ^ 1; B.depth = L.depth + 1; B.gcount = right_cnt;
-  A.ogh = B.ogh = -1;  // no leaf-ordered (gq, hq) copy: k_hist gathers them by row
   B.slot = R;
   V.leaves[leaf] = A;
   V.leaves[R] = B;
@@ -88,7 +87,6 @@ __device__ void part_expand(const DevView& V, int e, int leaf, const DevLeaf& L,
   DevLeaf A = L, B = L;  // A = left child, B = right child
   A.count = left_cnt; A.buf = L.buf ^ 1; A.depth = L.depth + 1;
   B.begin = L.begin + left_cnt; B.count = right_cnt; B.buf = L.buf ^ 1; B.depth = L.depth + 1;
-  A.ogh = B.ogh = -1;
   const DevSplit s = V.best[leaf];
   // SplitInner: on one GPU (update_cnt = true) the counts come from the partition; in data-parallel mode
   // (update_cnt = false, data_parallel_tree_learner.cpp:250-256) they stay the global, hessian-derived counts of
@@ -102,8 +100,8 @@ __device__ void part_expand(const DevView& V, int e, int leaf, const DevLeaf& L,
   // whose index depends on (round, item) only, so the host can address it blind (data-parallel all-reduce)
   const int fresh = 1 + (c->round - 1) * c->lookahead + e;
   int smaller;
-  if (gl < gr) { smaller = 0; A.slot = fresh; B.slot = L.slot; A.ogh = L.buf ^ 1; }
-  else { smaller = 1; B.slot = fresh; A.slot = L.slot; B.ogh = L.buf ^ 1; }  // the scatter wrote the smaller side's ordered (gq, hq)
+  if (gl < gr) { smaller = 0; A.slot = fresh; B.slot = L.slot; }
+  else { smaller = 1; B.slot = fresh; A.slot = L.slot; }  // the scatter wrote the smaller side's ordered (gq, hq)
   int skip = 0;
   if (V.p.max_depth > 0 && A.depth >= V.p.max_depth) skip = 1;
   if (!skip && gr < V.p.min_data_in_leaf * 2 && gl < V.p.min_data_in_leaf * 2) skip = 1;
@@ -294,15 +292,6 @@ __global__ void __launch_bounds__(PART_THREADS, PART_BLOCKS_PER_SM + 1) k_partit
     return;
   }
   const int left_total = total;
-  // Ordered gradients: the side that will be histogrammed (the smaller child: same rule as part_expand) also gets its
-  // rows' (gq, hq) pairs written in leaf order next to the indices, so that k_hist reads them contiguously.
-  int4* ogh_dst = nullptr; int ogh_side = -1;
-  if (mode == 0) {
-    int gl = left_total, gr = L.count - left_total;
-    if (V.data_parallel) { const DevSplit s = V.best[leaf]; gl = s.left_count; gr = s.right_count; }
-    ogh_side = gl < gr ? 0 : 1;
-    ogh_dst = V.ogh[L.buf ^ 1] + L.begin;
-  }
   int tile_off = before;
   for (int tile = t0; tile < t1; ++tile) {
     const int lt = tile - t0;
@@ -325,13 +314,10 @@ __global__ void __launch_bounds__(PART_THREADS, PART_BLOCKS_PER_SM + 1) k_partit
         const unsigned ltm = (1u << lane) - 1u;
         const int row = lt == 0 ? row0[r] : src[pos];
         if ((word >> lane) & 1u) {
-          const int p = tile_off + wpre + __popc(word & ltm);
-          dst[p] = row;
-          if (ogh_side == 0) ogh_dst[p] = V.gq[row];
+          dst[tile_off + wpre + __popc(word & ltm)] = row;
         } else {
           const int rights_before = (tile * PART_TILE - tile_off) + (w * 32 - wpre) + __popc(~word & ltm);
           dst[left_total + rights_before] = row;
-          if (ogh_side == 1) ogh_dst[left_total + rights_before] = V.gq[row];
         }
       }
     }

@@ -51,9 +51,7 @@ int lgbcu_valid_create(LgbCuContext* c, int32_t num_data, const uint8_t* bins, i
   ValidSet v;
   v.n = num_data;
   CU(dev_alloc(&v.d_bins, (size_t)num_data * c->stride));
-  if (c->stride == c->F) {
-    CU(cudaMemcpyAsync(v.d_bins, bins, (size_t)num_data * c->F, cudaMemcpyHostToDevice, c->stream));
-  } else {
+  {
     uint8_t* packed = nullptr;
     CU(dev_alloc(&packed, (size_t)num_data * c->F));
     CU(cudaMemcpyAsync(packed, bins, (size_t)num_data * c->F, cudaMemcpyHostToDevice, c->stream));

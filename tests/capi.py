@@ -8,7 +8,7 @@ import numpy as np
 
 ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
 REF_SO = os.path.join(ROOT, "oracle", "_ref", "lib_lightgbm.so")
-OURS_SO = os.path.join(ROOT, "lightgbmv1_b200", "lib_lightgbm_b200.so")
+OURS_SO = os.environ.get("LGBM_B200_LIB", os.path.join(ROOT, "lightgbmv1_b200", "lib_lightgbm_b200.so"))  # (override: debug builds, tools/build_dbg.sh)
 
 DTYPE_F32, DTYPE_F64, DTYPE_I32 = 0, 1, 2
 

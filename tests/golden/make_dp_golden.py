@@ -24,18 +24,24 @@ BASE = "objective=binary num_leaves=63 learning_rate=0.1 min_data_in_leaf=20 max
 OUT = os.path.join(HERE, "dp_reference_2rank_model.txt")
 
 
-def dp_case():
-    """the matrix, labels and shard bounds of the golden run"""
+def dp_case(sorted_shards=False):
+    """the matrix, labels and reference-dataset rows of the golden run.  sorted_shards=True (NOT used for the golden)
+    sorts the rows by a feature, so that class balance and feature ranges differ between the machines and some leaves
+    have no rows at all on one of them.  The reference cannot serve as the oracle for that case: with zero local rows
+    Dataset::ConstructHistograms returns before it clears the histogram buffer (include/LightGBM/dataset.h:508-510),
+    the stale contents of the pool slot enter the reduce-scatter, and its model depends on them (observed here: split
+    gains of 4.7e6 on 200 000 rows).  tests/test_multigpu.py uses the sorted case to compare this library's 2-rank run
+    with its own 1-rank run instead."""
     rng = np.random.default_rng(0)
     X = rng.standard_normal((N_ROWS, N_FEAT)).astype(np.float32)
     X[:, 21:25] = np.maximum(0, X[:, 21:25])
     X[:, 25:28] = np.array([0.0, 1.087, 2.173], dtype=np.float32)[rng.integers(0, 3, size=(N_ROWS, 3))]
     w = np.random.default_rng(1).standard_normal(N_FEAT)
     y = ((X @ w + 0.5 * X[:, 0] * X[:, 1] + rng.standard_normal(N_ROWS)) > 0).astype(np.float32)
-    # shards sorted by a feature: the classes and the feature ranges differ between the machines
-    order = np.argsort(X[:, 3], kind="stable")
-    X, y = np.ascontiguousarray(X[order]), np.ascontiguousarray(y[order])
-    # ... but the common reference dataset must see the whole range: a fixed stride sample
+    if sorted_shards:
+        order = np.argsort(X[:, 3], kind="stable")
+        X, y = np.ascontiguousarray(X[order]), np.ascontiguousarray(y[order])
+    # the common reference dataset must see the whole range: a fixed stride sample
     ref_rows = np.arange(0, N_ROWS, N_ROWS // REF_ROWS)[:REF_ROWS]
     return X, y, ref_rows
 

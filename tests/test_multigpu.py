@@ -1,12 +1,13 @@
 """tree_learner=data (A11).  The oracle is the reference's OWN data-parallel learner: 2 machines over localhost sockets,
 contiguous row shards binned against a common reference dataset (tests/golden/make_dp_golden.py wrote rank 0's model
-to tests/golden/dp_reference_2rank_model.txt).  The shards are sorted by a feature, so class balance and feature ranges
-differ between the machines and some leaves have no rows on one of them.
+to tests/golden/dp_reference_2rank_model.txt).
   (gpu, 1 GPU)      one rank with the data-parallel count semantics (LGBCU_FORCE_DP_COUNTS) on the unsharded matrix,
                     same bin mappers, must reproduce the reference's 2-machine model;
   (gpu, >= 2 GPUs)  the 2-rank NCCL run must reproduce it too -- and equal the 1-rank run bit for bit (the histogram
-                    all-reduce is an integer sum); with is_unbalance the label weights come from the class counts of
-                    ALL ranks (binary_objective.hpp:72-75);
+                    all-reduce is an integer sum); with shards SORTED by a feature (skewed classes, leaves with no
+                    rows on one rank -- a case the reference itself gets wrong, see make_dp_golden.dp_case) and
+                    is_unbalance (label weights from the class counts of ALL ranks, binary_objective.hpp:72-75) the
+                    2-rank run must still equal the 1-rank run;
   (cpu, gloo, world_size 2) the host-side shard plumbing: shards built against a common reference dataset carry the
                     same bin mappers and together hold exactly the bins of the unsharded matrix."""
 import ctypes as C
@@ -25,11 +26,13 @@ GOLDEN = os.path.join(H.ROOT, "tests", "golden", "dp_reference_2rank_model.txt")
 SCRIPT = os.path.join(H.ROOT, "tools", "run_dp.py")
 
 
-def _torchrun(nproc, port, out, extra=""):
+def _torchrun(nproc, port, out, extra="", sorted_shards=False):
     cmd = [sys.executable, "-m", "torch.distributed.run", "--nnodes=1", f"--nproc-per-node={nproc}",
            "--master-addr", "127.0.0.1", "--master-port", str(port), SCRIPT, "--out", out]
     if extra:
         cmd += ["--extra", extra]
+    if sorted_shards:
+        cmd += ["--sorted-shards"]
     subprocess.check_call(cmd, env=dict(os.environ), timeout=900)
 
 
@@ -60,13 +63,13 @@ def test_two_rank_model_equals_reference_two_machine_model_and_one_rank_model(tm
 
 
 @pytest.mark.gpu
-def test_two_rank_is_unbalance_uses_global_class_counts(tmp_path):
+def test_two_rank_sorted_shards_is_unbalance_equals_one_rank(tmp_path):
     if N.device_count() < 2:
         pytest.skip("needs 2 GPUs")
     one, two = str(tmp_path / "one.txt"), str(tmp_path / "two.txt")
-    subprocess.check_call([sys.executable, SCRIPT, "--out", one, "--extra", "is_unbalance=true"],
+    subprocess.check_call([sys.executable, SCRIPT, "--out", one, "--extra", "is_unbalance=true", "--sorted-shards"],
                           env=dict(os.environ, LGBCU_FORCE_DP_COUNTS="1"), timeout=600)
-    _torchrun(2, 29512, two, extra="is_unbalance=true")
+    _torchrun(2, 29512, two, extra="is_unbalance=true", sorted_shards=True)
     same, n, first = capi.compare_models(open(one).read(), open(two).read(), rtol_value=0.0)
     assert same == n, (same, n, first)
 

@@ -14,10 +14,11 @@ ap = argparse.ArgumentParser()
 ap.add_argument("--out", default="")
 ap.add_argument("--extra", default="", help="extra parameters, e.g. is_unbalance=true")
 ap.add_argument("--iters", type=int, default=G.ITERS)
+ap.add_argument("--sorted-shards", action="store_true", help="rows sorted by a feature: skewed shards, empty local leaves")
 args = ap.parse_args()
 rank = int(os.environ.get("RANK", "0")); world = int(os.environ.get("WORLD_SIZE", "1")); local = int(os.environ.get("LOCAL_RANK", "0"))
 
-X, y, ref_rows = G.dp_case()
+X, y, ref_rows = G.dp_case(sorted_shards=args.sorted_shards)
 n = len(y)
 ours = capi.ours(); lib = ours.lib
 base = G.BASE + (" " + args.extra if args.extra else "")
