@@ -168,6 +168,18 @@ LGBCU_API int lgbcu_add_score_by_tree(LgbCuContext* ctx, int32_t num_leaves, con
                                       const int32_t* left_child, const int32_t* right_child, const double* leaf_value,
                                       const int32_t* rows, int32_t num_rows, int64_t rows_tag);
 
+/* F3: bagging on the device (GBDT::Bagging + BaggingHelper, src/boosting/gbdt.cpp:162-181, 209-243): one LCG per
+ * 1024-row block (include/LightGBM/utils/random.h), seeded seed + block by lgbcu_bagging_reset (ResetBaggingConfig,
+ * gbdt.cpp:739-797); lgbcu_bagging draws the next bag -- a row is in the bag when its block's NextFloat() <
+ * fraction -- and keeps it on the device: in-bag rows ascending, then out-of-bag rows ascending.  Pass
+ * LGBCU_DEVICE_BAG as lgbcu_begin_tree's bag_indices / LGBCU_DEVICE_OOB as lgbcu_add_score_by_tree's rows to use it.
+ * lgbcu_copy_bag reads the whole list back (tests). */
+#define LGBCU_DEVICE_BAG ((const int32_t*)(intptr_t)-1)
+#define LGBCU_DEVICE_OOB ((const int32_t*)(intptr_t)-1)
+LGBCU_API int lgbcu_bagging_reset(LgbCuContext* ctx, int32_t seed);
+LGBCU_API int lgbcu_bagging(LgbCuContext* ctx, double fraction, int32_t* bag_count);
+LGBCU_API int lgbcu_copy_bag(LgbCuContext* ctx, int32_t* out, int32_t n);
+
 /* A8: BeforeTrain (src/treelearner/serial_tree_learner.cpp:244-272): reset partition / leaf table / pool,
  * root sums.  bag_indices==NULL -> all rows; feature_used==NULL -> all features (ColSampler by-tree mask). */
 LGBCU_API int lgbcu_begin_tree(LgbCuContext* ctx, const int32_t* bag_indices, int32_t bag_count,

@@ -72,7 +72,7 @@ LGBCU_SYMBOLS = [
     "lgbcu_set_score", "lgbcu_add_score_const", "lgbcu_copy_score", "lgbcu_add_score_by_partition", "lgbcu_add_score_by_tree",
     "lgbcu_begin_tree", "lgbcu_hist_build", "lgbcu_hist_read", "lgbcu_num_total_bin", "lgbcu_hist_subtract",
     "lgbcu_find_best_split", "lgbcu_partition", "lgbcu_leaf_indices", "lgbcu_set_leaf_sums",
-    "lgbcu_get_leaf_sums", "lgbcu_train_tree", "lgbcu_comm_unique_id", "lgbcu_comm_init", "lgbcu_comm_destroy", "lgbcu_comm_release_all", "lgbcu_comm_allreduce_sum_f64",
+    "lgbcu_get_leaf_sums", "lgbcu_train_tree", "lgbcu_comm_unique_id", "lgbcu_comm_init", "lgbcu_comm_destroy", "lgbcu_comm_release_all", "lgbcu_bagging_reset", "lgbcu_bagging", "lgbcu_copy_bag", "lgbcu_comm_allreduce_sum_f64",
     "lgbcu_profile_enable", "lgbcu_profile_read", "lgbcu_partition_rows_noalloc", "lgbcu_profile_phases", "lgbcu_pin_host_buffer", "lgbcu_unpin_host_buffer", "lgbcu_valid_create", "lgbcu_valid_set_label",
     "lgbcu_valid_set_weight", "lgbcu_valid_set_query", "lgbcu_valid_set_score", "lgbcu_valid_add_const", "lgbcu_valid_add_tree",
     "lgbcu_valid_copy_score", "lgbcu_eval_set_ndcg", "lgbcu_eval",
@@ -253,6 +253,26 @@ class CudaLearner:
         check(lib.lgbcu_begin_tree(self._h, None if bi is None else _ptr(bi, C.c_int32),
                                    C.c_int32(0 if bi is None else len(bi)),
                                    None if fu is None else _ptr(fu, C.c_int8)))
+
+    # ---- bagging on the device
+    DEVICE_BAG = C.cast(C.c_void_p(-1), C.POINTER(C.c_int32))
+
+    def bagging_reset(self, seed: int) -> None:
+        check(lib.lgbcu_bagging_reset(self._h, C.c_int32(seed)))
+
+    def bagging(self, fraction: float) -> int:
+        n = C.c_int32()
+        check(lib.lgbcu_bagging(self._h, C.c_double(fraction), C.byref(n)))
+        return n.value
+
+    def copy_bag(self, n: int) -> np.ndarray:
+        out = np.empty(n, dtype=np.int32)
+        check(lib.lgbcu_copy_bag(self._h, _ptr(out, C.c_int32), C.c_int32(n)))
+        return out
+
+    def begin_tree_device_bag(self, feature_used=None) -> None:
+        fu = None if feature_used is None else np.ascontiguousarray(feature_used, dtype=np.int8)
+        check(lib.lgbcu_begin_tree(self._h, self.DEVICE_BAG, C.c_int32(0), None if fu is None else _ptr(fu, C.c_int8)))
 
     def hist_build(self, leaf: int) -> None:
         check(lib.lgbcu_hist_build(self._h, C.c_int32(leaf)))

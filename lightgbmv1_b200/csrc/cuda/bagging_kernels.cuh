@@ -1,0 +1,117 @@
+// Bagging on the device (replaces GBDT::Bagging + BaggingHelper, src/boosting/gbdt.cpp:162-181,
+// 209-243): every 1024-row block draws from its own LCG (include/LightGBM/utils/random.h: x = 214013 x + 2531011,
+// NextFloat = ((x >> 16) & 0x7fff) / 32768), which makes the sample independent of the number of threads -- and lets a
+// GPU reproduce it exactly: a warp takes one block, lane l jumps the block's generator ahead by 32 l steps (an affine
+// map composed on the host) and draws the 32 numbers of rows [32 l, 32 l + 32), which become one ballot-style bit word.
+// A scan over the per-block counts and a stable scatter then write the in-bag rows (ascending) followed by the
+// out-of-bag rows (ascending) -- the list the tree grows on and the list the tree walk scores afterwards.  Nothing
+// crosses the PCIe bus but the bag size.
+#pragma once
+
+#define BAG_BLOCK 1024   /* GBDT::bagging_rand_block_ (gbdt.h:519) == PART_TILE: one bit-word row per generator */
+static_assert(BAG_BLOCK == PART_TILE, "one partition tile per bagging generator");
+
+struct BagJump { unsigned a[33], c[33]; };   // x_{32 l} = a[l] * x_0 + c[l]  (mod 2^32)
+
+__global__ void k_bag_seed(int nblock, int seed, unsigned* __restrict__ state) {
+  for (int b = blockIdx.x * blockDim.x + threadIdx.x; b < nblock; b += gridDim.x * blockDim.x) state[b] = (unsigned)(seed + b);
+}
+
+// one warp per 1024-row block
+__global__ void __launch_bounds__(256) k_bag_flags(int n, double fraction, BagJump J, unsigned* __restrict__ state,
+                                                   unsigned* __restrict__ bits, int* __restrict__ tile_left) {
+  const int lane = threadIdx.x & 31;
+  const int nblock = (n + BAG_BLOCK - 1) / BAG_BLOCK;
+  for (int b = blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5); b < nblock; b += gridDim.x * (blockDim.x >> 5)) {
+    const unsigned x0 = state[b];
+    unsigned x = J.a[lane] * x0 + J.c[lane];
+    unsigned word = 0;
+    const int row0 = b * BAG_BLOCK + lane * 32;
+#pragma unroll 8
+    for (int i = 0; i < 32; ++i) {
+      x = 214013u * x + 2531011u;
+      const float r = (float)((x >> 16) & 0x7FFFu) / 32768.0f;
+      if (row0 + i < n && (double)r < fraction) word |= 1u << i;
+    }
+    bits[(size_t)b * 32 + lane] = word;
+    int cnt = __popc(word);
+    for (int o = 16; o > 0; o >>= 1) cnt += __shfl_xor_sync(0xffffffffu, cnt, o);
+    __syncwarp();
+    if (lane == 0) {
+      tile_left[b] = cnt;
+      state[b] = J.a[32] * x0 + J.c[32];   // the generator after its 1024 draws (the reference draws for every row of the block)
+    }
+  }
+}
+
+// in-bag rows (ascending) to out[0, bag), out-of-bag rows (ascending) to out[bag, n)
+__global__ void __launch_bounds__(256) k_bag_scatter(int n, const unsigned* __restrict__ bits, const int* __restrict__ tile_off,
+                                                     const unsigned* __restrict__ ctl, int* __restrict__ out) {
+  const int lane = threadIdx.x & 31;
+  const int nblock = (n + BAG_BLOCK - 1) / BAG_BLOCK;
+  const int bag = (int)ctl[0];
+  for (int b = blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5); b < nblock; b += gridDim.x * (blockDim.x >> 5)) {
+    const unsigned word = bits[(size_t)b * 32 + lane];
+    const int pc = __popc(word);
+    int inc = pc;
+    for (int o = 1; o < 32; o <<= 1) { const int v = __shfl_up_sync(0xffffffffu, inc, o); if (lane >= o) inc += v; }
+    const int in_before = tile_off[b] + inc - pc;                  // in-bag rows before this lane's 32 rows
+    const int row0 = b * BAG_BLOCK + lane * 32;
+    int li = in_before, ri = bag + (row0 - in_before);
+    for (int i = 0; i < 32 && row0 + i < n; ++i) {
+      if ((word >> i) & 1u) out[li++] = row0 + i; else out[ri++] = row0 + i;
+    }
+  }
+}
+
+extern "C" {
+
+int lgbcu_bagging_reset(LgbCuContext* c, int32_t seed) {
+  NEED(c && c->N > 0, "lgbcu_bagging_reset: dataset not set");
+  CU(cudaSetDevice(c->device));
+  const int nblock = (c->N + BAG_BLOCK - 1) / BAG_BLOCK;
+  CU(dev_alloc(&c->d_bag_state, (size_t)nblock));
+  CU(dev_alloc(&c->d_bag_bits, (size_t)nblock * 32));
+  CU(dev_alloc(&c->d_bag_tile, (size_t)nblock));
+  CU(dev_alloc(&c->d_bag_ctl, (size_t)2));
+  CU(dev_alloc(&c->d_bag, (size_t)c->N));
+  LAUNCH(k_bag_seed, grid_for(c, nblock, 256), 256, 0, c->stream, nblock, (int)seed, c->d_bag_state);
+  CU(cudaGetLastError());
+  c->bag_count = c->N; c->bag_ready = false;
+  return 0;
+}
+
+int lgbcu_bagging(LgbCuContext* c, double fraction, int32_t* bag_count) {
+  NEED(c && bag_count, "lgbcu_bagging: NULL argument");
+  NEED(c->d_bag_state, "lgbcu_bagging: call lgbcu_bagging_reset first");
+  CU(cudaSetDevice(c->device));
+  BagJump J;
+  {  // affine maps of the LCG for 32 l steps, l = 0..32
+    unsigned a32 = 1, c32 = 0;
+    for (int i = 0; i < 32; ++i) { c32 = 214013u * c32 + 2531011u; a32 = 214013u * a32; }
+    unsigned a = 1, cc = 0;
+    for (int l = 0; l <= 32; ++l) { J.a[l] = a; J.c[l] = cc; cc = a32 * cc + c32; a = a32 * a; }
+  }
+  const int nblock = (c->N + BAG_BLOCK - 1) / BAG_BLOCK;
+  const int grid = grid_for(c, (long long)nblock * 32, 256);
+  LAUNCH(k_bag_flags, grid, 256, 0, c->stream, c->N, fraction, J, c->d_bag_state, c->d_bag_bits, c->d_bag_tile);
+  LAUNCH(k_na_scan, 1, 1024, 0, c->stream, c->d_bag_tile, c->N, c->d_bag_ctl, reinterpret_cast<int*>(c->d_bag_ctl + 1));
+  LAUNCH(k_bag_scatter, grid, 256, 0, c->stream, c->N, c->d_bag_bits, c->d_bag_tile, c->d_bag_ctl, c->d_bag);
+  CU(cudaGetLastError());
+  CU(cudaMemcpyAsync(c->h_ctl, c->d_bag_ctl, sizeof(unsigned), cudaMemcpyDeviceToHost, c->stream));
+  CU(cudaStreamSynchronize(c->stream));
+  c->bag_count = (int)*reinterpret_cast<unsigned*>(c->h_ctl);
+  c->bag_ready = true;
+  *bag_count = c->bag_count;
+  return 0;
+}
+
+int lgbcu_copy_bag(LgbCuContext* c, int32_t* out, int32_t n) {
+  NEED(c && out && n == c->N && c->bag_ready, "lgbcu_copy_bag: bad argument / no bag drawn");
+  CU(cudaSetDevice(c->device));
+  CU(cudaMemcpyAsync(out, c->d_bag, sizeof(int) * (size_t)n, cudaMemcpyDeviceToHost, c->stream));
+  CU(cudaStreamSynchronize(c->stream));
+  return 0;
+}
+
+}  // extern "C"

@@ -118,6 +118,9 @@ struct LgbCuContext {
   unsigned* d_part_bits = nullptr;
   unsigned long long* d_part_sync = nullptr;
   uint8_t* d_bins_col = nullptr; long long col_stride = 0;
+  // device-side bagging (bagging_kernels.cuh)
+  unsigned* d_bag_state = nullptr; unsigned* d_bag_bits = nullptr; int* d_bag_tile = nullptr; unsigned* d_bag_ctl = nullptr;
+  int* d_bag = nullptr; int bag_count = 0; bool bag_ready = false;
   // query structure (lambdarank)
   int* d_query = nullptr; int num_queries = 0; int max_query = 0;
   std::vector<int> h_query;
@@ -431,7 +434,8 @@ int lgbcu_destroy(LgbCuContext* c) {
                   c->d_indices[0], c->d_indices[1], c->d_part_bits, c->d_part_sync, c->d_bins_col, c->d_query, c->d_label_gain,
                   c->d_inv_max_dcg, c->d_sigmoid_table, c->d_pool, c->d_splittable, c->d_leaves, c->d_best,
                   c->d_feat_best, c->d_ctl, c->d_records, c->d_leaf_value, c->d_export, c->d_tree_i32, c->d_tree_i8,
-                  c->d_tree_f64, c->d_rows, c->d_scratch, c->d_parent_split, c->d_mfb_fix, c->d_feat_key, c->d_leaf_key, c->d_spec, c->d_expanded};
+                  c->d_tree_f64, c->d_rows, c->d_scratch, c->d_parent_split, c->d_mfb_fix, c->d_feat_key, c->d_leaf_key, c->d_spec, c->d_expanded,
+                  c->d_bag_state, c->d_bag_bits, c->d_bag_tile, c->d_bag_ctl, c->d_bag};
   for (void* p : ptrs) if (p) cudaFree(p);
   if (c->h_records) cudaFreeHost(c->h_records);
   if (c->h_ctl) cudaFreeHost(c->h_ctl);
@@ -774,16 +778,18 @@ int lgbcu_add_score_by_tree(LgbCuContext* c, int32_t num_leaves, const int32_t* 
   NEED(c && c->N > 0, "lgbcu_add_score_by_tree: dataset not set");
   NEED(num_leaves >= 1 && leaf_value, "lgbcu_add_score_by_tree: bad tree");
   CU(cudaSetDevice(c->device));
-  const int n = rows ? num_rows : c->N;
+  const bool device_oob = rows == LGBCU_DEVICE_OOB;   // the out-of-bag tail of the bag lgbcu_bagging drew
+  if (device_oob) { NEED(c->bag_ready, "lgbcu_add_score_by_tree: no bag has been drawn"); rows = nullptr; num_rows = c->N - c->bag_count; }
+  const int n = (rows || device_oob) ? num_rows : c->N;
   if (n <= 0) return 0;
   if (num_leaves == 1) {  // constant tree: score += leaf_value[0] (tree.cpp:110-118)
     if (leaf_value[0] == 0.0) return 0;
-    NEED(rows == nullptr, "lgbcu_add_score_by_tree: constant tree over a row subset is not supported");
+    NEED(rows == nullptr && !device_oob, "lgbcu_add_score_by_tree: constant tree over a row subset is not supported");
     return lgbcu_add_score_const(c, leaf_value[0]);
   }
   TreeDev T;
   if (upload_tree(c, num_leaves, split_feature_inner, threshold_bin, decision_type, left_child, right_child, leaf_value, &T)) return -1;
-  const int* d_rows = nullptr;
+  const int* d_rows = device_oob ? c->d_bag + c->bag_count : nullptr;
   if (rows) {
     const bool reuse = rows_tag != 0 && rows_tag == c->rows_tag && num_rows == c->rows_count;
     if (!reuse) {
@@ -804,7 +810,13 @@ int lgbcu_begin_tree(LgbCuContext* c, const int32_t* bag_indices, int32_t bag_co
   CU(cudaSetDevice(c->device));
   if (ensure_tree_buffers(c)) return -1;
   int identity = 1;
-  if (bag_indices) {
+  if (bag_indices == LGBCU_DEVICE_BAG) {   // the bag lgbcu_bagging drew, already on the device
+    NEED(c->bag_ready, "lgbcu_begin_tree: no bag has been drawn (lgbcu_bagging)");
+    CU(cudaMemcpyAsync(c->d_indices[0], c->d_bag, sizeof(int) * (size_t)c->bag_count, cudaMemcpyDeviceToDevice, c->stream));
+    c->root_count = c->bag_count;
+    identity = 0;
+    bag_indices = nullptr;
+  } else if (bag_indices) {
     NEED(bag_count > 0 && bag_count <= c->N, "lgbcu_begin_tree: bag_count %d out of range", bag_count);
     CU(cudaMemcpyAsync(c->d_indices[0], bag_indices, sizeof(int) * bag_count, cudaMemcpyHostToDevice, c->stream));
     c->root_count = bag_count;
@@ -1198,3 +1210,5 @@ int lgbcu_comm_destroy(LgbCuContext* c) {  // detach: the communicator itself st
 #include "valid_eval.cuh"
 
 #include "noalloc_partition.cuh"
+
+#include "bagging_kernels.cuh"

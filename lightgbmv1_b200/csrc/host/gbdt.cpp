@@ -20,7 +20,6 @@ namespace {
 void Check(int rc) {
   if (rc != 0) Log::Fatal("%s", lgbcu_last_error());
 }
-const int kBaggingRandBlock = 1024;  // gbdt.h:519
 // LGBM_B200_TIMING=1: wall-clock of the host-side stages on stderr (where does an end-to-end call spend its time)
 struct StageTimer {
   bool on; std::chrono::steady_clock::time_point t;
@@ -108,8 +107,8 @@ GBDT::GBDT(const Dataset* train, const Config& config)
   // ---- ResetBaggingConfig (gbdt.cpp:739-797)
   if (config_.bagging_fraction < 1.0 && config_.bagging_freq > 0) {
     bag_cnt_ = static_cast<data_size_t>(config_.bagging_fraction * N);
-    bag_indices_.resize(N);
-    for (int i = 0; i < (N + kBaggingRandBlock - 1) / kBaggingRandBlock; ++i) bagging_rands_.emplace_back(config_.bagging_seed + i);
+    Check(lgbcu_bagging_reset(ctx_, config_.bagging_seed));  // one generator per 1024-row block, seeded bagging_seed + block
+    use_bagging_ = true;
     need_re_bagging_ = true;
   }
   // ---- ColSampler::SetTrainingData (col_sampler.hpp:39-53): note the sample drawn here is discarded by the
@@ -141,24 +140,16 @@ void GBDT::ResetFeatureMask() {
   for (int i : pick) feature_used_[train_->inner_feature_index(valid_features_[i])] = 1;
 }
 
-// GBDT::Bagging + BaggingHelper (gbdt.cpp:162-181, 209-243): one Random per 1024-row block, rows kept in order
+// GBDT::Bagging (gbdt.cpp:209-243): the draw itself (BaggingHelper, one generator per 1024-row block) runs on the
+// device and the bag stays there; the host only learns its size
 void GBDT::Bagging(int iter) {
   const int N = train_->num_data();
+  if (!use_bagging_) return;
   if (!((bag_cnt_ < N && config_.bagging_freq > 0 && iter % config_.bagging_freq == 0) || need_re_bagging_)) return;
-  if (bagging_rands_.empty()) return;
   need_re_bagging_ = false;
-  const int nblock = static_cast<int>(bagging_rands_.size());
-  std::vector<uint8_t> in_bag(N);
-#pragma omp parallel for schedule(static)
-  for (int b = 0; b < nblock; ++b) {
-    const int s = b * kBaggingRandBlock, e = std::min(N, s + kBaggingRandBlock);
-    for (int i = s; i < e; ++i) in_bag[i] = bagging_rands_[b].NextFloat() < config_.bagging_fraction;
-  }
-  data_size_t l = 0;
-  for (int i = 0; i < N; ++i) if (in_bag[i]) bag_indices_[l++] = i;
-  bag_cnt_ = l;
-  for (int i = 0; i < N; ++i) if (!in_bag[i]) bag_indices_[l++] = i;
-  ++bag_version_;
+  int32_t cnt = 0;
+  Check(lgbcu_bagging(ctx_, config_.bagging_fraction, &cnt));
+  bag_cnt_ = cnt;
   Log::Debug("Re-bagging, using %d data to train", bag_cnt_);
 }
 
@@ -191,10 +182,10 @@ bool GBDT::TrainOneIter(const float* grad, const float* hess) {
 
   std::unique_ptr<Tree> tree(new Tree(2));
   bool should_continue = false;
-  const bool bagged = !bag_indices_.empty() && bag_cnt_ < N;
+  const bool bagged = use_bagging_ && bag_cnt_ < N;
   if (class_need_train_) {
     ResetFeatureMask();  // BeforeTrain: col_sampler_.ResetByTree()
-    Check(lgbcu_begin_tree(ctx_, bagged ? bag_indices_.data() : nullptr, bagged ? bag_cnt_ : 0,
+    Check(lgbcu_begin_tree(ctx_, bagged ? LGBCU_DEVICE_BAG : nullptr, bagged ? bag_cnt_ : 0,
                            need_reset_bytree_ ? feature_used_.data() : nullptr));
     int ns = 0;
     st.tick("gradients/bagging/begin_tree");
@@ -218,7 +209,7 @@ bool GBDT::TrainOneIter(const float* grad, const float* hess) {
       std::vector<int> thr(tree->threshold_in_bin().begin(), tree->threshold_in_bin().end());
       Check(lgbcu_add_score_by_tree(ctx_, tree->num_leaves(), tree->split_feature_inner().data(), thr.data(),
                                     tree->decision_type().data(), tree->left_child().data(), tree->right_child().data(),
-                                    tree->leaf_values().data(), bag_indices_.data() + bag_cnt_, N - bag_cnt_, bag_version_));
+                                    tree->leaf_values().data(), LGBCU_DEVICE_OOB, N - bag_cnt_, 0));
     }
     AddTreeToValid(*tree);
     if (std::fabs(init_score) > kEpsilon) tree->AddBias(init_score);

@@ -71,11 +71,9 @@ class GBDT {
   bool data_parallel_ = false;  // this booster trains over the NCCL communicator (tree_learner=data, num_machines > 1)
   bool class_need_train_ = true;
   // bagging (gbdt.cpp:209-243, 739-797)
-  std::vector<data_size_t> bag_indices_;  // in-bag (ascending) then out-of-bag (ascending)
-  data_size_t bag_cnt_;
-  std::vector<Random> bagging_rands_;
+  data_size_t bag_cnt_;     // the bag itself (in-bag rows ascending, then out-of-bag rows) lives on the device
+  bool use_bagging_ = false;
   bool need_re_bagging_ = false;
-  int64_t bag_version_ = 0;
   // column sampling (col_sampler.hpp)
   Random feature_rand_;
   std::vector<int> valid_features_;  // real indices of used features

@@ -174,9 +174,11 @@ def train(lib, X, y, params, iters, weight=None, group=None, init_score=None, ds
     return ds, b, done
 
 
-def compare_models(text_a, text_b, rtol_value=1e-9, allow_near_ties=True):
+def compare_models(text_a, text_b, rtol_value=1e-9, allow_near_ties=True, stop_at_first=True):
     """Structure (split_feature, threshold, decision_type, children, leaf_count) must be identical tree by tree;
-    leaf values / weights within rtol.  Returns (num_trees_identical, num_trees, first_mismatch_description)."""
+    leaf values / weights within rtol.  Returns (num_trees_identical, num_trees, first_mismatch_description).
+    stop_at_first=True counts the identical PREFIX (a differing tree changes the gradients of every later one);
+    False counts every identical tree (a near-tie that picks an equivalent threshold leaves the later trees equal)."""
     ta, tb = parse_trees(text_a), parse_trees(text_b)
     n = min(len(ta), len(tb))
     same = 0
@@ -202,6 +204,6 @@ def compare_models(text_a, text_b, rtol_value=1e-9, allow_near_ties=True):
                     break
         if ok:
             same += 1
-        else:
+        elif stop_at_first:
             break  # later trees depend on this one
     return same, n, first
