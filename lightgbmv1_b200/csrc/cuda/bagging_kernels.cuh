@@ -11,7 +11,7 @@
 #define BAG_BLOCK 1024   /* GBDT::bagging_rand_block_ (gbdt.h:519) == PART_TILE: one bit-word row per generator */
 static_assert(BAG_BLOCK == PART_TILE, "one partition tile per bagging generator");
 
-struct BagJump { unsigned a[33], c[33]; };   // x_{32 l} = a[l] * x_0 + c[l]  (mod 2^32)
+struct BagJump { unsigned a[32], c[32]; };   // x_{32 l} = a[l] * x_0 + c[l]  (mod 2^32)
 
 __global__ void k_bag_seed(int nblock, int seed, unsigned* __restrict__ state) {
   for (int b = blockIdx.x * blockDim.x + threadIdx.x; b < nblock; b += gridDim.x * blockDim.x) state[b] = (unsigned)(seed + b);
@@ -25,22 +25,23 @@ __global__ void __launch_bounds__(256) k_bag_flags(int n, double fraction, BagJu
   for (int b = blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5); b < nblock; b += gridDim.x * (blockDim.x >> 5)) {
     const unsigned x0 = state[b];
     unsigned x = J.a[lane] * x0 + J.c[lane];
-    unsigned word = 0;
+    unsigned word = 0, x_last = x;
     const int row0 = b * BAG_BLOCK + lane * 32;
 #pragma unroll 8
     for (int i = 0; i < 32; ++i) {
       x = 214013u * x + 2531011u;
       const float r = (float)((x >> 16) & 0x7FFFu) / 32768.0f;
-      if (row0 + i < n && (double)r < fraction) word |= 1u << i;
+      if (row0 + i < n) { x_last = x; if ((double)r < fraction) word |= 1u << i; }
     }
     bits[(size_t)b * 32 + lane] = word;
     int cnt = __popc(word);
     for (int o = 16; o > 0; o >>= 1) cnt += __shfl_xor_sync(0xffffffffu, cnt, o);
     __syncwarp();
-    if (lane == 0) {
-      tile_left[b] = cnt;
-      state[b] = J.a[32] * x0 + J.c[32];   // the generator after its 1024 draws (the reference draws for every row of the block)
-    }
+    if (lane == 0) tile_left[b] = cnt;
+    // the generator has drawn once per EXISTING row of its block (the last block of the data may be partial): the lane
+    // that owns the block's last row holds its state
+    const int rows_here = min(BAG_BLOCK, n - b * BAG_BLOCK);
+    if (lane == (rows_here - 1) / 32) state[b] = x_last;
   }
 }
 
@@ -86,11 +87,11 @@ int lgbcu_bagging(LgbCuContext* c, double fraction, int32_t* bag_count) {
   NEED(c->d_bag_state, "lgbcu_bagging: call lgbcu_bagging_reset first");
   CU(cudaSetDevice(c->device));
   BagJump J;
-  {  // affine maps of the LCG for 32 l steps, l = 0..32
+  {  // affine maps of the LCG for 32 l steps, l = 0..31
     unsigned a32 = 1, c32 = 0;
     for (int i = 0; i < 32; ++i) { c32 = 214013u * c32 + 2531011u; a32 = 214013u * a32; }
     unsigned a = 1, cc = 0;
-    for (int l = 0; l <= 32; ++l) { J.a[l] = a; J.c[l] = cc; cc = a32 * cc + c32; a = a32 * a; }
+    for (int l = 0; l < 32; ++l) { J.a[l] = a; J.c[l] = cc; cc = a32 * cc + c32; a = a32 * a; }
   }
   const int nblock = (c->N + BAG_BLOCK - 1) / BAG_BLOCK;
   const int grid = grid_for(c, (long long)nblock * 32, 256);

@@ -95,6 +95,7 @@ struct DevCtl {
   int kg, kh;        // fixed-point exponents
   double scale_g, scale_h, inv_g, inv_h;
   unsigned feat_done;  // "last block done" counter of k_find_split
+  unsigned row_done[2 * LGB_KMAX];  // ... and one per row of its grid (one scanned leaf): blocks of that row that are done
   unsigned part_epoch[LGB_KMAX];  // per item: launches of k_partition so far (tags the words of V.part_sync); never reset
   unsigned bar_arrive[LGB_KMAX], bar_base[LGB_KMAX];  // k_partition, per item: blocks arrived so far (monotonic) / value when the launch began
   long long global_root;  // root rows over all ranks   } adjacent: one 2 x int64 sum all-reduce

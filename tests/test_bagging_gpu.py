@@ -20,10 +20,13 @@ class BlockLCG:
     def draw(self, fraction):
         in_bag = np.zeros(self.nblock * 1024, dtype=bool)
         x = self.x.copy()
-        for i in range(1024):   # every generator draws for every row of its block, in row order
-            x = (np.uint64(214013) * x + np.uint64(2531011)) & np.uint64(0xffffffff)
+        rows_in_block = np.minimum(1024, self.n - 1024 * np.arange(self.nblock))
+        for i in range(1024):   # a generator draws once per existing row of its block, in row order
+            live = i < rows_in_block
+            nx = (np.uint64(214013) * x + np.uint64(2531011)) & np.uint64(0xffffffff)
+            x = np.where(live, nx, x)
             r = ((x >> np.uint64(16)) & np.uint64(0x7fff)).astype(np.float32) / np.float32(32768.0)
-            in_bag[i::1024][:self.nblock] = r.astype(np.float64) < fraction
+            in_bag[i::1024][:self.nblock] = live & (r.astype(np.float64) < fraction)
         self.x = x
         in_bag = in_bag.reshape(self.nblock, 1024).reshape(-1)[:self.n]
         rows = np.arange(self.n, dtype=np.int32)
