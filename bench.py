@@ -12,10 +12,13 @@ A "step" is one boosting iteration (gradients -> 254 x {histogram, split search,
 `value`  : iterations/s with everything resident in HBM (that is how the API works: the matrix is uploaded once by
            LGBM_BoosterCreate); K synchronous calls, each ending in a stream sync + device->host read of the
            split records, bracketed by barrier + device sync, max over ranks.
-`e2e`    : the same K iterations INCLUDING LGBM_BoosterCreate (host->device upload of the binned matrix + labels)
-           and a final LGBM_BoosterGetPredict (device->host read of all training scores), divided by K:
-           what a C-API user pays from host buffers.  h2d/d2h bytes are per step (total / K).  The data-parallel
-           rendezvous (LGBM_NetworkInitNCCL) is made once per process, as the reference's Network::Init is.
+`e2e`    : the same K iterations from HOST buffers: LGBM_DatasetCreateFromMat on the float32 matrix (bin mappers on a
+           host sample, host->device copy of the raw matrix, value->bin on the device), LGBM_DatasetSetField(label),
+           LGBM_BoosterCreate, K x LGBM_BoosterUpdateOneIter and a final LGBM_BoosterGetPredict (device->host read of all
+           training scores), divided by K: what a C-API user pays.  h2d/d2h bytes are per step (total / K).  The
+           reference arm's `e2e` is timed from the same call (its `value` stays the iterations alone).  The
+           data-parallel rendezvous (LGBM_NetworkInitNCCL) and the common reference dataset of the shards are made
+           once per process, as the reference's Network::Init is.
 `roofline`: the histogram kernel k_hist ALONE (CUDA events around the kernel, not around the all-reduce that follows
            it in data-parallel runs), algorithmic bytes per SURVEY 8(d) (n*(G+8) [+4n if indexed] + total_bin*16 per
            call), measured in a separate profiled pass after the timed region.
@@ -144,6 +147,16 @@ def run_reference(args):
         ref.update(b)
     dt = time.perf_counter() - t0
     v = args.steps / dt
+    ref.booster_free(b); ref.dataset_free(ds)
+    # e2e: the same K iterations from the host matrix (LGBM_DatasetCreateFromMat .. LGBM_BoosterGetPredict), / K
+    t0 = time.perf_counter()
+    ds = ref.dataset_from_mat(X, params)
+    ref.set_field(ds, "label", y)
+    b = ref.booster_create(ds, params)
+    for _ in range(args.steps):
+        ref.update(b)
+    ref.get_predict(b, n)
+    e2e_dt = time.perf_counter() - t0
     line = {
         "impl": "reference", "metric": "boosting iters/sec", "value": v, "unit": "iters/s", "n_gpus": args.gpus,
         "steps": args.steps, "warmup": args.warmup, "ms_per_step": 1e3 * dt / args.steps, "higher_is_better": True,
@@ -151,7 +164,9 @@ def run_reference(args):
         "config": config_of(n),
         "cpu_baseline": {"value": v, "unit": "iters/s", "cores": cores, "kind": "reference",
                          "sample": f"full workload, {args.steps} iterations after {args.warmup} warm-up, force_col_wise"},
-        "e2e": {"value": v, "unit": "iters/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
+        "e2e": {"value": args.steps / e2e_dt, "unit": "iters/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0,
+                "what": "LGBM_DatasetCreateFromMat + SetField(label) + LGBM_BoosterCreate + K x LGBM_BoosterUpdateOneIter + "
+                        "LGBM_BoosterGetPredict, / K (all on the host cores)", "iterations_only": v},
     }
     emit(line)
     return 0
@@ -181,13 +196,13 @@ def run_ours(args):
     ds_full = None
     if use_dist:
         # identical bin mappers on every rank: a reference dataset from the first 200k rows, then this rank's shard
-        ref_ds = ours.dataset_from_mat(X[:200_000], ds_params)
+        ref_ds = ours.dataset_from_mat(X[:200_000], ds_params + f" gpu_device_id={local}")
         lo, hi = rank * n // world, (rank + 1) * n // world
         Xs, ys = np.ascontiguousarray(X[lo:hi]), np.ascontiguousarray(y[lo:hi])
-        ds = ours.dataset_from_mat(Xs, ds_params, reference=ref_ds)
+        ds = ours.dataset_from_mat(Xs, ds_params + f" gpu_device_id={local}", reference=ref_ds)
         ours.set_field(ds, "label", ys)
         if rank == 0:   # the unsharded matrix with the same mappers, for the N-rank == 1-rank check
-            ds_full = ours.dataset_from_mat(X, ds_params, reference=ref_ds)
+            ds_full = ours.dataset_from_mat(X, ds_params + f" gpu_device_id={local}", reference=ref_ds)
             ours.set_field(ds_full, "label", y)
         # the rendezvous is made ONCE per process (the reference's Network::Init, src/network/network.cpp:45-58):
         # rank 0 creates the NCCL id, torch.distributed carries it; every booster of this process trains over it
@@ -201,12 +216,11 @@ def run_ours(args):
         params = ds_params + f" tree_learner=data num_machines={world} gpu_device_id={local}"
         local_rows = hi - lo
     else:
-        ds = ours.dataset_from_mat(X, ds_params)
+        ds = ours.dataset_from_mat(X, ds_params + f" gpu_device_id={local}")
         ours.set_field(ds, "label", y)
         params = ds_params + f" gpu_device_id={local}"
         local_rows = n
-    if not (world == 1 and not args.no_cpu_baseline):
-        del X
+    X_e2e = None if use_dist else X
 
     def barrier():
         if use_dist:
@@ -221,18 +235,26 @@ def run_ours(args):
         ours.update(b)
         ours.booster_free(b)
 
-    # ---- e2e pass: BoosterCreate (H2D of the binned matrix + labels) + K iterations + GetPredict (D2H scores)
+    # ---- e2e pass, from host buffers: DatasetCreateFromMat (H2D of the raw float matrix, binned on the device) +
+    # SetField(label) + BoosterCreate + K iterations + GetPredict (D2H of all scores)
     barrier()
     t0 = time.perf_counter()
-    b = ours.booster_create(ds, params)
+    if use_dist:
+        ds_e = ours.dataset_from_mat(Xs, ds_params + f" gpu_device_id={local}", reference=ref_ds)
+        ours.set_field(ds_e, "label", ys)
+    else:
+        ds_e = ours.dataset_from_mat(X_e2e, ds_params + f" gpu_device_id={local}")
+        ours.set_field(ds_e, "label", y)
+    b = ours.booster_create(ds_e, params)
     for _ in range(args.steps):
         ours.update(b)
     scores = ours.get_predict(b, local_rows)
     barrier()
     e2e_dt = time.perf_counter() - t0
-    h2d_total = local_rows * (N_FEAT + 4)  # binned matrix (as passed by the host) + float labels
+    h2d_total = local_rows * (N_FEAT * 4 + 4)  # the raw float32 matrix + float labels
     d2h_total = local_rows * 8
     ours.booster_free(b)
+    ours.dataset_free(ds_e)
     del scores
 
     # ---- timed pass: W warm-up + exactly K iterations, device-resident
@@ -353,7 +375,8 @@ def run_ours(args):
         "clocks": clocks,
         "e2e": {"value": args.steps / e2e_dt, "unit": "iters/s", "h2d_bytes_per_step": h2d_total / args.steps,
                 "d2h_bytes_per_step": d2h_total / args.steps,
-                "what": "LGBM_BoosterCreate (upload) + K x LGBM_BoosterUpdateOneIter + LGBM_BoosterGetPredict, / K"},
+                "what": "LGBM_DatasetCreateFromMat (host sample -> bin mappers, H2D of the float32 matrix, value->bin on the device) + "
+                        "SetField(label) + LGBM_BoosterCreate + K x LGBM_BoosterUpdateOneIter + LGBM_BoosterGetPredict, / K"},
         "gpu_launches": int(launches),
         "roofline": {"bound": "hbm", "kernel": "k_hist (block-shared sub-histogram of 32 features, lane = feature, one byte load per (row, lane), "
                                                "32-bit shared atomic pairs, DSMEM cluster reduce; global-atomic path for leaves < 256 rows)",

@@ -131,6 +131,30 @@ LGBCU_API int lgbcu_set_dataset(LgbCuContext* ctx, int32_t num_data, int32_t num
  * reference's DenseBin uses; the transpose to row-major happens on device. */
 LGBCU_API int lgbcu_set_dataset_columns(LgbCuContext* ctx, int32_t num_data, int32_t num_features,
                                         const uint8_t* const* columns, const LgbCuFeatureMeta* meta);
+/* F1: value -> bin on the device (the row push loop of LGBM_DatasetCreateFromMat, src/c_api.cpp:1082-1097 ->
+ * BinMapper::ValueToBin, include/LightGBM/bin.h:457-495).  The host finds the bin mappers on its sample
+ * (BinMapper::FindBin); this call uploads the raw matrix once (float32 data_type 0 / float64 data_type 1, row- or
+ * column-major) and bins every (row, inner feature) with the reference's binary search over the feature's upper
+ * bounds (upper_bounds[bound_offset .. bound_offset + num_bin)) -- bit-identical to the host map.  The result, a
+ * row-major [nrow][num_features] matrix of stored values, stays on the device: lgbcu_set_dataset_binned makes it a
+ * learner's resident matrix without a host round trip, lgbcu_binned_copy_to_host reads it back. */
+typedef struct LgbCuBinnedMatrix LgbCuBinnedMatrix;
+typedef struct LgbCuBinFeature {
+  int32_t column;         /* column of the raw matrix */
+  int32_t num_bin;        /* BinMapper::num_bin() */
+  int32_t most_freq_bin;
+  int32_t missing_type;   /* LGBCU_MISSING_* */
+  int32_t bound_offset;   /* first upper bound of this feature in upper_bounds */
+  int32_t reserved;
+} LgbCuBinFeature;
+LGBCU_API int lgbcu_bin_matrix(int device, const void* data, int data_type, int32_t nrow, int32_t ncol, int is_row_major,
+                               int32_t num_features, const LgbCuBinFeature* feats, const double* upper_bounds,
+                               int32_t num_bounds, LgbCuBinnedMatrix** out);
+LGBCU_API int lgbcu_binned_copy_to_host(LgbCuBinnedMatrix* m, uint8_t* out);
+LGBCU_API int lgbcu_binned_device(const LgbCuBinnedMatrix* m, int* device);
+LGBCU_API int lgbcu_binned_free(LgbCuBinnedMatrix* m);
+LGBCU_API int lgbcu_set_dataset_binned(LgbCuContext* ctx, const LgbCuBinnedMatrix* m, const LgbCuFeatureMeta* meta);
+
 LGBCU_API int lgbcu_set_tree_params(LgbCuContext* ctx, const LgbCuTreeParams* params);
 LGBCU_API int lgbcu_set_hist_mode(LgbCuContext* ctx, int mode);
 

@@ -1,0 +1,178 @@
+// Value -> bin on the device (replaces the row push loop of LGBM_DatasetCreateFromMat,
+// src/c_api.cpp:1082-1097 -> FeatureGroup::PushData -> BinMapper::ValueToBin, include/LightGBM/bin.h:457-495).
+// The host keeps what is sequential and tiny (sampling, BinMapper::FindBin); the N x F map runs here: one thread per
+// (row, inner feature) does the reference's binary search over the feature's upper bounds -- same comparisons, in
+// double, so the result is bit-identical -- and stores the single-feature-group encoding (0 = most frequent bin,
+// else bin + 1 - [most_freq_bin == 0]; feature_group.h:153-165).  The raw matrix crosses PCIe once, in chunks staged
+// through two page-locked buffers (filled by the host threads while the previous chunk is in flight).
+#pragma once
+
+struct LgbCuBinnedMatrix {
+  int device = 0; int32_t nrow = 0, nfeat = 0;
+  uint8_t* d_bins = nullptr;     // [nrow][nfeat] stored values, row-major, no padding
+};
+
+struct BinFeatDev { int column, num_bin, mfb, missing_type, bound_off, pad; };
+
+template <typename T>
+__global__ void __launch_bounds__(256) k_bin_rows(const T* __restrict__ x, long long rows, int ncol, int row_major, long long ld,
+                                                  int F, const BinFeatDev* __restrict__ feats, const double* __restrict__ bounds,
+                                                  uint8_t* __restrict__ out) {
+  const long long total = rows * F;
+  for (long long i = blockIdx.x * (long long)blockDim.x + threadIdx.x; i < total; i += (long long)gridDim.x * blockDim.x) {
+    const long long r = i / F;
+    const int f = (int)(i - r * F);
+    const BinFeatDev d = feats[f];
+    double value = (double)(row_major ? x[r * ncol + d.column] : x[(long long)d.column * ld + r]);
+    int bin;
+    if (value != value && d.missing_type == LGBCU_MISSING_NAN) {
+      bin = d.num_bin - 1;
+    } else {
+      if (value != value) value = 0.0;
+      int l = 0, rr = d.num_bin - 1;
+      if (d.missing_type == LGBCU_MISSING_NAN) rr -= 1;
+      const double* ub = bounds + d.bound_off;
+      while (l < rr) {
+        const int m = (rr + l - 1) / 2;
+        if (value <= ub[m]) rr = m; else l = m + 1;
+      }
+      bin = l;
+    }
+    int stored = 0;
+    if (bin != d.mfb) stored = bin + (d.mfb == 0 ? 0 : 1);   // bin + 1 - [mfb == 0]
+    out[i] = (uint8_t)stored;
+  }
+}
+
+extern "C" {
+
+int lgbcu_binned_free(LgbCuBinnedMatrix* m) {
+  if (!m) return 0;
+  cudaSetDevice(m->device);
+  if (m->d_bins) cudaFree(m->d_bins);
+  delete m;
+  return 0;
+}
+
+int lgbcu_bin_matrix(int device, const void* data, int data_type, int32_t nrow, int32_t ncol, int is_row_major,
+                     int32_t num_features, const LgbCuBinFeature* feats, const double* upper_bounds,
+                     int32_t num_bounds, LgbCuBinnedMatrix** out) {
+  NEED(data && feats && upper_bounds && out, "lgbcu_bin_matrix: NULL argument");
+  NEED(nrow > 0 && ncol > 0 && num_features > 0, "lgbcu_bin_matrix: empty matrix");
+  NEED(data_type == 0 || data_type == 1, "lgbcu_bin_matrix: data_type must be 0 (float32) or 1 (float64)");
+  int ndev = 0;
+  if (cudaGetDeviceCount(&ndev) != cudaSuccess || ndev == 0) { cudaGetLastError(); return fail("lgbcu_bin_matrix: no CUDA device available"); }
+  NEED(device >= 0 && device < ndev, "lgbcu_bin_matrix: device %d out of range (have %d)", device, ndev);
+  CU(cudaSetDevice(device));
+  struct Guard {   // everything but the result is released on every way out
+    void* dev[4] = {nullptr, nullptr, nullptr, nullptr}; void* pin[2] = {nullptr, nullptr};
+    cudaStream_t s[2] = {nullptr, nullptr}; cudaEvent_t ev[2] = {nullptr, nullptr}; LgbCuBinnedMatrix* m = nullptr;
+    ~Guard() {
+      for (void* p : dev) if (p) cudaFree(p);
+      for (void* p : pin) if (p) cudaFreeHost(p);
+      for (auto e : ev) if (e) cudaEventDestroy(e);
+      for (auto st : s) if (st) cudaStreamDestroy(st);
+      if (m) lgbcu_binned_free(m);
+    }
+  } G;
+  const size_t esz = data_type == 0 ? 4 : 8;
+  std::vector<BinFeatDev> hf(num_features);
+  for (int f = 0; f < num_features; ++f) {
+    NEED(feats[f].column >= 0 && feats[f].column < ncol && feats[f].num_bin >= 1 && feats[f].bound_offset >= 0 &&
+         feats[f].bound_offset + feats[f].num_bin <= num_bounds, "lgbcu_bin_matrix: bad descriptor of feature %d", f);
+    hf[f] = BinFeatDev{feats[f].column, feats[f].num_bin, feats[f].most_freq_bin, feats[f].missing_type, feats[f].bound_offset, 0};
+  }
+  BinFeatDev* d_feats = nullptr; double* d_bounds = nullptr;
+  CU(cudaMalloc(&G.dev[0], sizeof(BinFeatDev) * num_features)); d_feats = static_cast<BinFeatDev*>(G.dev[0]);
+  CU(cudaMalloc(&G.dev[1], sizeof(double) * num_bounds)); d_bounds = static_cast<double*>(G.dev[1]);
+  CU(cudaMemcpy(d_feats, hf.data(), sizeof(BinFeatDev) * num_features, cudaMemcpyHostToDevice));
+  CU(cudaMemcpy(d_bounds, upper_bounds, sizeof(double) * num_bounds, cudaMemcpyHostToDevice));
+  G.m = new LgbCuBinnedMatrix();
+  G.m->device = device; G.m->nrow = nrow; G.m->nfeat = num_features;
+  CU(cudaMalloc(reinterpret_cast<void**>(&G.m->d_bins), (size_t)nrow * num_features));
+  for (int i = 0; i < 2; ++i) { CU(cudaStreamCreateWithFlags(&G.s[i], cudaStreamNonBlocking)); CU(cudaEventCreateWithFlags(&G.ev[i], cudaEventDisableTiming)); }
+  cudaDeviceProp prop; CU(cudaGetDeviceProperties(&prop, device));
+  const int max_grid = prop.multiProcessorCount * 16;
+  static const int hw = [] { const long n = sysconf(_SC_NPROCESSORS_ONLN); return n > 0 ? (int)n : 1; }();
+  const int nthreads = std::max(omp_get_max_threads(), std::min(8, hw));
+  if (is_row_major) {
+    // chunks of whole rows: host threads copy a chunk into a page-locked buffer while the previous one is in flight
+    const size_t row_bytes = (size_t)ncol * esz;
+    const size_t chunk_rows = std::max<size_t>(1, std::min<size_t>((size_t)nrow, ((size_t)64 << 20) / row_bytes));
+    for (int i = 0; i < 2; ++i) { CU(cudaMallocHost(&G.pin[i], chunk_rows * row_bytes)); CU(cudaMalloc(&G.dev[2 + i], chunk_rows * row_bytes)); }
+    int k = 0;
+    for (size_t r0 = 0; r0 < (size_t)nrow; r0 += chunk_rows, ++k) {
+      const int b = k & 1;
+      const size_t rows = std::min(chunk_rows, (size_t)nrow - r0);
+      CU(cudaEventSynchronize(G.ev[b]));   // the copy that last used this staging buffer has finished (no-op the first time)
+      const char* src = static_cast<const char*>(data) + r0 * row_bytes;
+      const size_t bytes = rows * row_bytes;
+      const long long pieces = (long long)((bytes + ((size_t)1 << 20) - 1) >> 20);
+#pragma omp parallel for schedule(static) num_threads(nthreads)
+      for (long long p = 0; p < pieces; ++p) {
+        const size_t a = (size_t)p << 20, e = std::min(bytes, a + ((size_t)1 << 20));
+        std::memcpy(static_cast<char*>(G.pin[b]) + a, src + a, e - a);
+      }
+      CU(cudaMemcpyAsync(G.dev[2 + b], G.pin[b], bytes, cudaMemcpyHostToDevice, G.s[b]));
+      CU(cudaEventRecord(G.ev[b], G.s[b]));
+      const long long work = (long long)rows * num_features;
+      const int grid = (int)std::min<long long>(max_grid, (work + 255) / 256);
+      uint8_t* dst = G.m->d_bins + r0 * num_features;
+      if (data_type == 0) k_bin_rows<float><<<grid, 256, 0, G.s[b]>>>(static_cast<const float*>(G.dev[2 + b]), (long long)rows, ncol, 1, 0, num_features, d_feats, d_bounds, dst);
+      else k_bin_rows<double><<<grid, 256, 0, G.s[b]>>>(static_cast<const double*>(G.dev[2 + b]), (long long)rows, ncol, 1, 0, num_features, d_feats, d_bounds, dst);
+      g_launches.fetch_add(1, std::memory_order_relaxed);
+      CU(cudaGetLastError());
+    }
+  } else {
+    // column-major input: upload the used columns only, whole, then one launch
+    const size_t col_bytes = (size_t)nrow * esz;
+    CU(cudaMalloc(&G.dev[2], col_bytes * num_features));
+    std::vector<BinFeatDev> hc = hf;
+    for (int f = 0; f < num_features; ++f) {
+      CU(cudaMemcpyAsync(static_cast<char*>(G.dev[2]) + f * col_bytes, static_cast<const char*>(data) + (size_t)hf[f].column * col_bytes,
+                         col_bytes, cudaMemcpyHostToDevice, G.s[0]));
+      hc[f].column = f;
+    }
+    CU(cudaMemcpyAsync(d_feats, hc.data(), sizeof(BinFeatDev) * num_features, cudaMemcpyHostToDevice, G.s[0]));
+    const long long work = (long long)nrow * num_features;
+    const int grid = (int)std::min<long long>(max_grid, (work + 255) / 256);
+    if (data_type == 0) k_bin_rows<float><<<grid, 256, 0, G.s[0]>>>(static_cast<const float*>(G.dev[2]), (long long)nrow, num_features, 0, (long long)nrow, num_features, d_feats, d_bounds, G.m->d_bins);
+    else k_bin_rows<double><<<grid, 256, 0, G.s[0]>>>(static_cast<const double*>(G.dev[2]), (long long)nrow, num_features, 0, (long long)nrow, num_features, d_feats, d_bounds, G.m->d_bins);
+    g_launches.fetch_add(1, std::memory_order_relaxed);
+    CU(cudaGetLastError());
+  }
+  CU(cudaStreamSynchronize(G.s[0]));
+  CU(cudaStreamSynchronize(G.s[1]));
+  *out = G.m;
+  G.m = nullptr;
+  return 0;
+}
+
+int lgbcu_binned_copy_to_host(LgbCuBinnedMatrix* m, uint8_t* out) {
+  NEED(m && out, "lgbcu_binned_copy_to_host: NULL argument");
+  CU(cudaSetDevice(m->device));
+  CU(cudaMemcpy(out, m->d_bins, (size_t)m->nrow * m->nfeat, cudaMemcpyDeviceToHost));
+  return 0;
+}
+
+int lgbcu_binned_device(const LgbCuBinnedMatrix* m, int* device) {
+  NEED(m && device, "lgbcu_binned_device: NULL argument");
+  *device = m->device;
+  return 0;
+}
+
+// A2 from a matrix that is already on the device (binned by lgbcu_bin_matrix): no host round trip
+int lgbcu_set_dataset_binned(LgbCuContext* c, const LgbCuBinnedMatrix* m, const LgbCuFeatureMeta* meta) {
+  NEED(c && m && meta, "lgbcu_set_dataset_binned: NULL argument");
+  NEED(m->device == c->device, "lgbcu_set_dataset_binned: the matrix lives on device %d, the learner on device %d", m->device, c->device);
+  if (setup_dataset_common(c, m->nrow, m->nfeat, meta)) return -1;
+  LAUNCH(k_pad_rows, grid_for(c, (long long)m->nrow * (c->stride / 4), 256), 256, 0, c->stream, (long long)m->nrow,
+         m->nfeat, c->stride, m->d_bins, c->d_bins);
+  LAUNCH(k_transpose_bins, grid_for(c, m->nrow, 256), 256, 0, c->stream, m->nrow, m->nfeat, c->stride, c->d_bins,
+         c->d_bins_col, c->col_stride);
+  CU(cudaGetLastError());
+  CU(cudaStreamSynchronize(c->stream));
+  return 0;
+}
+
+}  // extern "C"

@@ -65,7 +65,7 @@ struct DevLeaf {     // DataPartition range + LeafSplits + pool slot of one leaf
 // the largest gains side by side (the kernels of a round are latency bound, so K leaves cost about as much as one),
 // then commits, in the reference's order, every leaf whose turn has come and whose children are ready.  An expansion
 // is only wasted if the leaf budget runs out before the leaf's turn.
-#define LGB_KMAX 32
+#define LGB_KMAX 16
 
 struct DevSpec {     // an expanded leaf that is not committed yet: what Split + two FindBestThreshold runs produced
   DevLeaf child[2];  // [0] = left (keeps the parent's leaf id when committed), [1] = right (gets the next free id)
@@ -95,7 +95,6 @@ struct DevCtl {
   int kg, kh;        // fixed-point exponents
   double scale_g, scale_h, inv_g, inv_h;
   unsigned feat_done;  // "last block done" counter of k_find_split
-  unsigned row_done[2 * LGB_KMAX];  // ... and one per row of its grid (one scanned leaf): blocks of that row that are done
   unsigned part_epoch[LGB_KMAX];  // per item: launches of k_partition so far (tags the words of V.part_sync); never reset
   unsigned bar_arrive[LGB_KMAX], bar_base[LGB_KMAX];  // k_partition, per item: blocks arrived so far (monotonic) / value when the launch began
   long long global_root;  // root rows over all ranks   } adjacent: one 2 x int64 sum all-reduce
@@ -113,10 +112,7 @@ struct DevParams {   // LgbCuTreeParams + derived switches
 struct DevView {
   int num_data, num_features, row_stride, total_bin, num_tiles16;
   int data_parallel;         // 1: histograms are all-reduced across ranks, leaf counts are the global estimates
-  int rec_off;               // byte offset of the (g, h) record inside a row of `bins`
-  uint8_t* bins;             // [num_data][row_stride]: the row's stored bins, then (at rec_off) its 16-byte fixed-point
-                             // (g, h) record of the current tree (pack_gh, written by k_quantise): one 64-byte DRAM burst
-                             // serves both when the histogram kernel gathers a row of an indexed leaf
+  const uint8_t* bins;
   const uint8_t* bins_col;   // column-major copy [F][col_stride]: the partition of a large leaf reads one feature of
   long long col_stride;      // (nearly) consecutive rows -- 32 rows per sector instead of one
   const DevFeat* feats;
@@ -128,7 +124,8 @@ struct DevView {
   int pool_slots;            // histogram slots in the pool
   long long bits_stride;     // words of part_bits per item
   double2* mfb_fix;          // [num_leaves slots][num_features] FixHistogram'd most-frequent-bin entry, in double
-  const int4* gq;            // [num_data] contiguous copy of the records: what the full-data root pass streams
+  const float2* gh;          // [num_data] interleaved (gradient, hessian) of the current iteration, written by k_absmax: 84 MB at
+                             // 10.5M rows, so it stays L2-resident while a tree grows; converted to fixed point when a row is staged
   int* indices[2];
   HistEntry* pool;           // [num_leaves][total_bin]
   DevLeaf* leaves;

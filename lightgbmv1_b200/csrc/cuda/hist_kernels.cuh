@@ -2,7 +2,7 @@
 // DenseBin::ConstructHistogramInner, src/io/dense_bin.hpp:97-140).
 //
 // Arithmetic: gradients/hessians (float) are converted once per tree to 64-bit fixed point with a per-tree
-// power-of-two scale (DevCtl::scale_g/scale_h, k_quantise; at most 47 value bits per row) and summed with integer
+// power-of-two scale (DevCtl::scale_g/scale_h; at most 47 value bits per row) by the lane that stages the row, and summed with integer
 // adds.  Integer sums are exact and order independent, so a histogram is bit-reproducible for any grid shape, any
 // number of GPUs and any atomic ordering, parent - sibling is exact, and the data-parallel all-reduce is exact; the
 // only rounding is the per-row quantisation (<= 2^-39 of max|g| for 10^7 rows).
@@ -22,9 +22,8 @@
 //                    Each wrap is seen by exactly the add that caused it and addition commutes, so (hi, lo) after
 //                    the block barrier is the exact 64-bit sum whatever the interleaving.
 //                    Feeding the lanes: a warp stages 32 rows at a time -- lane j loads row index j of the batch
-//                    (coalesced) and that row's fixed-point (g, h) record (it lies in the row's own slot of the bin
-//                    matrix, so the 64-byte DRAM burst that brings the bins brings it too; the full-data root pass
-//                    streams a contiguous copy instead) into shared memory;
+//                    (coalesced) and that row's fixed-point (g, h) record (gathered by row; contiguous for the
+//                    full-data root pass) into shared memory;
 //                    every lane then reads one 16-byte broadcast per row (row offset, g low, h low, packed high
 //                    words) and fetches ITS OWN bin of that row straight from the row-major matrix (32 lanes x 1 byte =
 //                    the row's 32-byte sector, one L1 wavefront, 16 loads in flight per warp): no transposition
@@ -55,6 +54,10 @@ __device__ unsigned long long g_hist_cycles[8];
 #define HSTAGE(i) do {} while (0)
 #endif
 
+__device__ __forceinline__ i64 to_fixed(float v, double scale) {
+  return __double2ll_rn((double)v * scale);
+}
+
 __device__ __forceinline__ void atomic_add_i64(i64* addr, i64 v) {
   atomicAdd(reinterpret_cast<unsigned long long*>(addr), (unsigned long long)v);
 }
@@ -68,11 +71,6 @@ __device__ __forceinline__ int4 pack_gh(i64 g, i64 h) {
 __device__ __forceinline__ i64 unpack_g(const int4& r) { return ((i64)(short)(r.z & 0xffff) << 32) | (unsigned)r.x; }
 __device__ __forceinline__ i64 unpack_h(const int4& r) { return ((i64)(r.z >> 16) << 32) | (unsigned)r.y; }
 
-// a row's record, from the row's own slot in the bin matrix (the same 64-byte burst as its bins)
-__device__ __forceinline__ int4 row_record(const DevView& V, int row) {
-  return *reinterpret_cast<const int4*>(V.bins + (size_t)row * V.row_stride + V.rec_off);
-}
-
 __device__ void hist_global_path(const DevView& V, const DevLeaf& L, bool identity, int bid, int nblocks) {
   const int* idx = V.indices[L.buf] + L.begin;
   HistEntry* out = V.pool + (size_t)L.slot * V.total_bin;
@@ -83,8 +81,8 @@ __device__ void hist_global_path(const DevView& V, const DevLeaf& L, bool identi
     const int ck = (int)(p - (long long)pos * nchunk);
     const int row = identity ? pos : idx[pos];
     const uint4 q = *reinterpret_cast<const uint4*>(V.bins + (size_t)row * V.row_stride + ck * 16);
-    const int4 gh = row_record(V, row);
-    const i64 gq = unpack_g(gh), hq = unpack_h(gh);
+    const float2 gh = V.gh[row];
+    const i64 gq = to_fixed(gh.x, V.ctl->scale_g), hq = to_fixed(gh.y, V.ctl->scale_h);
     const unsigned w[4] = {q.x, q.y, q.z, q.w};
 #pragma unroll
     for (int k = 0; k < 16; ++k) {
@@ -154,6 +152,7 @@ __device__ void hist_shared_path(const DevView& V, const DevLeaf& L, bool identi
   const int* idx = V.indices[L.buf] + L.begin;
   HistEntry* out = V.pool + (size_t)L.slot * V.total_bin;
   const unsigned stride16 = (unsigned)V.row_stride / 16u;  // row offsets travel as 32-bit counts of 16 bytes (64 GB)
+  const double sg = V.ctl->scale_g, sh = V.ctl->scale_h;
 #ifdef LGBCU_STAGE_TIMERS
   long long ht_ = clock64();
 #endif
@@ -173,7 +172,8 @@ __device__ void hist_shared_path(const DevView& V, const DevLeaf& L, bool identi
       const int pos = base + lane;
       if (pos < b1) {
         const int row = identity ? pos : idx[pos];
-        const int4 r = identity ? V.gq[pos] : row_record(V, row);
+        const float2 gh = V.gh[row];
+        const int4 r = pack_gh(to_fixed(gh.x, sg), to_fixed(gh.y, sh));
         nst = make_int4((int)((unsigned)row * stride16), r.x, r.y, r.z);
       }
     }
@@ -193,7 +193,8 @@ __device__ void hist_shared_path(const DevView& V, const DevLeaf& L, bool identi
         const int pos1 = base + step + lane;
         if (pos1 < b1) {
           const int row = identity ? pos1 : idx[pos1];
-          const int4 r = identity ? V.gq[pos1] : row_record(V, row);
+          const float2 gh = V.gh[row];
+          const int4 r = pack_gh(to_fixed(gh.x, sg), to_fixed(gh.y, sh));
           nst = make_int4((int)((unsigned)row * stride16), r.x, r.y, r.z);
         }
       }

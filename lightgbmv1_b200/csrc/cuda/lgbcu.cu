@@ -108,8 +108,7 @@ struct LgbCuContext {
   std::vector<DevFeat> h_feats;
   int8_t* d_feat_used = nullptr;
   // per-row state
-  int4* d_gq = nullptr;  // fixed-point (g, h) records of the current tree, contiguous (the rows of d_bins hold a copy)
-  int rec_off = 0;
+  float2* d_gh = nullptr;  // interleaved (g, h) of the current iteration
   float *d_grad = nullptr, *d_hess = nullptr, *d_label = nullptr, *d_weight = nullptr;
   bool has_weight = false, has_label = false;
   double* d_score = nullptr;
@@ -174,7 +173,7 @@ struct LgbCuContext {
     V.bins = d_bins; V.feats = d_feats; V.feat_used = d_feat_used; V.splittable = d_splittable;
     V.parent_split = d_parent_split; V.mfb_fix = d_mfb_fix; V.spec = d_spec; V.expanded = d_expanded; V.pool_slots = pool_slots;
     V.bits_stride = bits_stride; V.part_sync_stride = part_sync_stride;
-    V.gq = d_gq; V.rec_off = rec_off; V.indices[0] = d_indices[0]; V.indices[1] = d_indices[1];
+    V.gh = d_gh; V.indices[0] = d_indices[0]; V.indices[1] = d_indices[1];
     V.pool = d_pool; V.leaves = d_leaves; V.best = d_best; V.feat_best = d_feat_best; V.feat_key = d_feat_key; V.leaf_key = d_leaf_key; V.ctl = d_ctl;
     V.records = d_records; V.part_sync = d_part_sync; V.bins_col = d_bins_col; V.col_stride = col_stride; V.part_bits = d_part_bits; V.p = params;
     V.data_parallel = (comm != nullptr || force_dp_counts) ? 1 : 0;
@@ -373,6 +372,7 @@ int lgbcu_create(int device_id, LgbCuContext** out) {
   NEED(device_id >= 0 && device_id < n, "lgbcu_create: device %d out of range (have %d)", device_id, n);
   CU(cudaSetDevice(device_id));
   LgbCuContext* c = new LgbCuContext();
+  struct Guard { LgbCuContext* c; ~Guard() { if (c) lgbcu_destroy(c); } } guard{c};   // a failure below frees the half-built context
   c->device = device_id;
   cudaDeviceProp prop;
   CU(cudaGetDeviceProperties(&prop, device_id));
@@ -419,6 +419,7 @@ int lgbcu_create(int device_id, LgbCuContext** out) {
     if (const char* e = std::getenv("LGBCU_GRAPH_COMM")) c->graph_comm = std::atoi(e) != 0;
     if (const char* e = std::getenv("LGBCU_FORCE_DP_COUNTS")) c->force_dp_counts = std::atoi(e) != 0;
   }
+  guard.c = nullptr;
   *out = c;
   return 0;
 }
@@ -426,11 +427,11 @@ int lgbcu_create(int device_id, LgbCuContext** out) {
 int lgbcu_destroy(LgbCuContext* c) {
   if (!c) return 0;
   cudaSetDevice(c->device);
-  cudaStreamSynchronize(c->stream);
+  if (c->stream) cudaStreamSynchronize(c->stream);
   drop_graph(c);
   lgbcu_comm_destroy(c);
   free_valid_sets(c);
-  void* ptrs[] = {c->d_bins, c->d_feats, c->d_feat_used, c->d_grad, c->d_hess, c->d_gq, c->d_label, c->d_weight, c->d_score,
+  void* ptrs[] = {c->d_bins, c->d_feats, c->d_feat_used, c->d_grad, c->d_hess, c->d_gh, c->d_label, c->d_weight, c->d_score,
                   c->d_indices[0], c->d_indices[1], c->d_part_bits, c->d_part_sync, c->d_bins_col, c->d_query, c->d_label_gain,
                   c->d_inv_max_dcg, c->d_sigmoid_table, c->d_pool, c->d_splittable, c->d_leaves, c->d_best,
                   c->d_feat_best, c->d_ctl, c->d_records, c->d_leaf_value, c->d_export, c->d_tree_i32, c->d_tree_i8,
@@ -443,7 +444,7 @@ int lgbcu_destroy(LgbCuContext* c) {
   if (c->h_split) cudaFreeHost(c->h_split);
   for (int i = 0; i < 2; ++i) { if (c->h_stage[i]) cudaFreeHost(c->h_stage[i]); if (c->stage_ev[i]) cudaEventDestroy(c->stage_ev[i]); }
   for (auto e : c->ev) cudaEventDestroy(e);
-  cudaStreamDestroy(c->stream);
+  if (c->stream) cudaStreamDestroy(c->stream);
   delete c;
   return 0;
 }
@@ -460,11 +461,8 @@ static int setup_dataset_common(LgbCuContext* c, int32_t num_data, int32_t num_f
   NEED(num_features < (1 << KEY_FEAT_BITS), "lgbcu_set_dataset: %d features exceed the supported %d", num_features, (1 << KEY_FEAT_BITS) - 1);
   CU(cudaSetDevice(c->device));
   c->N = num_data; c->F = num_features;
-  // a row = its stored bins (padded to 16 bytes), then the 16-byte (g, h) record of the current tree; rows are whole
-  // 32-byte sectors and at least one 64-byte DRAM burst, so that gathering a row never straddles more than it must
-  c->rec_off = (num_features + 15) & ~15;
-  c->ntiles16 = c->rec_off / 16;
-  c->stride = std::max(64, (c->rec_off + 16 + 31) & ~31);
+  c->stride = (num_features + 15) & ~15;
+  c->ntiles16 = c->stride / 16;
   c->h_feats.resize(num_features);
   int base = 0;
   for (int f = 0; f < num_features; ++f) {
@@ -493,7 +491,7 @@ static int setup_dataset_common(LgbCuContext* c, int32_t num_data, int32_t num_f
   CU(cudaMemsetAsync(c->d_parent_split, 1, (size_t)LGB_KMAX * num_features, c->stream));
   CU(dev_alloc(&c->d_grad, (size_t)num_data));
   CU(dev_alloc(&c->d_hess, (size_t)num_data));
-  CU(dev_alloc(&c->d_gq, (size_t)num_data));
+  CU(dev_alloc(&c->d_gh, (size_t)num_data));
   CU(dev_alloc(&c->d_score, (size_t)num_data));
   CU(cudaMemsetAsync(c->d_score, 0, sizeof(double) * num_data, c->stream));
   CU(dev_alloc(&c->d_indices[0], (size_t)num_data));
@@ -519,14 +517,13 @@ int lgbcu_set_dataset(LgbCuContext* c, int32_t num_data, int32_t num_features, c
   {
     // one contiguous H2D copy, then pad rows to the 16-byte stride on the device (a strided 2-D copy of 28-byte rows
     // crawls: one DMA descriptor per row)
-    uint8_t* packed = nullptr;
-    CU(dev_alloc(&packed, (size_t)num_data * num_features));
-    CU(cudaMemcpyAsync(packed, bins, (size_t)num_data * num_features, cudaMemcpyHostToDevice, c->stream));
+    struct Tmp { uint8_t* p = nullptr; ~Tmp() { if (p) cudaFree(p); } } packed;   // released on every way out
+    CU(dev_alloc(&packed.p, (size_t)num_data * num_features));
+    CU(cudaMemcpyAsync(packed.p, bins, (size_t)num_data * num_features, cudaMemcpyHostToDevice, c->stream));
     LAUNCH(k_pad_rows, grid_for(c, (long long)num_data * (c->stride / 4), 256), 256, 0, c->stream, (long long)num_data,
-           num_features, c->stride, packed, c->d_bins);
+           num_features, c->stride, packed.p, c->d_bins);
     CU(cudaGetLastError());
     CU(cudaStreamSynchronize(c->stream));
-    cudaFree(packed);
   }
   LAUNCH(k_transpose_bins, grid_for(c, num_data, 256), 256, 0, c->stream, num_data, num_features, c->stride, c->d_bins,
          c->d_bins_col, c->col_stride);
@@ -540,7 +537,8 @@ int lgbcu_set_dataset_columns(LgbCuContext* c, int32_t num_data, int32_t num_fea
   NEED(columns, "lgbcu_set_dataset_columns: columns is NULL");
   if (setup_dataset_common(c, num_data, num_features, meta)) return -1;
   CU(cudaMemsetAsync(c->d_bins, 0, (size_t)num_data * c->stride, c->stream));
-  uint8_t* tmp[2] = {nullptr, nullptr};
+  struct Tmp { uint8_t* p[2] = {nullptr, nullptr}; ~Tmp() { for (auto q : p) if (q) cudaFree(q); } } T;   // released on every way out
+  uint8_t** tmp = T.p;
   CU(dev_alloc(&tmp[0], (size_t)num_data));
   CU(dev_alloc(&tmp[1], (size_t)num_data));
   for (int f = 0; f < num_features; ++f) {
@@ -553,7 +551,6 @@ int lgbcu_set_dataset_columns(LgbCuContext* c, int32_t num_data, int32_t num_fea
          c->d_bins_col, c->col_stride);
   CU(cudaGetLastError());
   CU(cudaStreamSynchronize(c->stream));
-  cudaFree(tmp[0]); cudaFree(tmp[1]);
   return 0;
 }
 
@@ -833,11 +830,9 @@ int lgbcu_begin_tree(LgbCuContext* c, const int32_t* bag_indices, int32_t bag_co
   // only the root's slot: every later slot is zeroed by the partition launch that hands it out
   CU(cudaMemsetAsync(c->d_pool, 0, sizeof(HistEntry) * (size_t)c->total_bin, c->stream));
   LAUNCH(k_reset_ctl_max, 1, 1, 0, c->stream, c->d_ctl, c->root_count, c->N);
-  LAUNCH(k_absmax, grid_for(c, c->N, 256), 256, 0, c->stream, c->N, c->d_grad, c->d_hess, c->d_ctl);
+  LAUNCH(k_absmax, grid_for(c, c->N, 256), 256, 0, c->stream, c->N, c->d_grad, c->d_hess, c->d_gh, c->d_ctl);
   if (comm_allreduce_tree_setup(c)) return -1;
   LAUNCH(k_prepare_tree, 1, 256, 0, c->stream, c->view(), c->root_count, identity, c->lookahead);
-  LAUNCH(k_quantise, grid_for(c, c->root_count, 256), 256, 0, c->stream, c->N, c->d_grad, c->d_hess, c->d_ctl, c->d_gq,
-         c->d_bins, c->stride, c->rec_off, identity ? nullptr : c->d_indices[0], c->root_count);
   CU(cudaGetLastError());
   if (bag_indices || feature_used) CU(cudaStreamSynchronize(c->stream));  // caller may reuse its buffers
   c->tree_begun = true;
@@ -1212,3 +1207,5 @@ int lgbcu_comm_destroy(LgbCuContext* c) {  // detach: the communicator itself st
 #include "noalloc_partition.cuh"
 
 #include "bagging_kernels.cuh"
+
+#include "binning_kernels.cuh"

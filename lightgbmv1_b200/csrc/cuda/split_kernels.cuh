@@ -696,46 +696,25 @@ __device__ int best_open_leaf(const DevView& V, int nl, int want_expanded, const
 // one warp: expansion of `leaf` -> leaf table, with the right child's id R and the record index given
 __device__ void commit_leaf_as(const DevView& V, int leaf, int R, int record_index, int lane) {
   DevSpec* S = &V.spec[leaf];
-  // every load first (the split that was applied, both children, their best splits and keys), then the stores: one
-  // memory round trip instead of one per copy
-  const int* sb = reinterpret_cast<const int*>(&V.best[leaf]);
-  const int* c0 = reinterpret_cast<const int*>(&S->child[0]);
-  const int* c1 = reinterpret_cast<const int*>(&S->child[1]);
-  const int* b0 = reinterpret_cast<const int*>(&S->best[0]);
-  const int* b1 = reinterpret_cast<const int*>(&S->best[1]);
-  const int* k0 = reinterpret_cast<const int*>(&S->key[0]);   // key[0], key[1] are adjacent: 8 words
-  int w_sb = 0, w_c0 = 0, w_c1 = 0, w_b0 = 0, w_b1 = 0, w_k = 0;
-  if (lane < DEVSPLIT_WORDS) { w_sb = __ldcg(sb + lane); w_b0 = __ldcg(b0 + lane); w_b1 = __ldcg(b1 + lane); }
-  if (lane < DEVLEAF_WORDS) { w_c0 = __ldcg(c0 + lane); w_c1 = __ldcg(c1 + lane); }
-  if (lane < 8) w_k = __ldcg(k0 + lane);
-  // the record: fields of the applied split + the children's global counts (DevLeaf::gcount)
-  {
-    const int gcl = __shfl_sync(FULL_MASK, w_c0, (int)(offsetof(DevLeaf, gcount) / 4));
-    const int gcr = __shfl_sync(FULL_MASK, w_c1, (int)(offsetof(DevLeaf, gcount) / 4));
-    // DevSplit words of the applied split, gathered into lane 0
-    int sw[DEVSPLIT_WORDS];
-#pragma unroll
-    for (int k = 0; k < DEVSPLIT_WORDS; ++k) sw[k] = __shfl_sync(FULL_MASK, w_sb, k);
-    if (lane == 0) {
-      DevSplit s;
-      int* sp = reinterpret_cast<int*>(&s);
-#pragma unroll
-      for (int k = 0; k < DEVSPLIT_WORDS; ++k) sp[k] = sw[k];
-      LgbCuSplitRecord rec;
-      rec.leaf = leaf; rec.right_leaf = R; rec.feature = s.feature; rec.real_feature = s.real_feature;
-      rec.threshold = s.threshold; rec.default_left = s.default_left;
-      rec.left_count = gcl; rec.right_count = gcr;
-      rec.gain = (float)(s.gain + V.p.min_gain_to_split); rec.reserved = 0;
-      rec.left_output = s.left_output; rec.right_output = s.right_output;
-      rec.left_sum_hessian = s.left_sum_h; rec.right_sum_hessian = s.right_sum_h;
-      rec.left_sum_gradient = s.left_sum_g; rec.right_sum_gradient = s.right_sum_g;
-      V.records[record_index] = rec;
-    }
+  if (lane == 0) {
+    const DevSplit s = V.best[leaf];  // the split that was applied
+    LgbCuSplitRecord rec;
+    rec.leaf = leaf; rec.right_leaf = R; rec.feature = s.feature; rec.real_feature = s.real_feature;
+    rec.threshold = s.threshold; rec.default_left = s.default_left;
+    rec.left_count = S->child[0].gcount; rec.right_count = S->child[1].gcount;
+    rec.gain = (float)(s.gain + V.p.min_gain_to_split); rec.reserved = 0;
+    rec.left_output = s.left_output; rec.right_output = s.right_output;
+    rec.left_sum_hessian = s.left_sum_h; rec.right_sum_hessian = s.right_sum_h;
+    rec.left_sum_gradient = s.left_sum_g; rec.right_sum_gradient = s.right_sum_g;
+    V.records[record_index] = rec;
   }
-  if (lane < DEVLEAF_WORDS) { reinterpret_cast<int*>(&V.leaves[leaf])[lane] = w_c0; reinterpret_cast<int*>(&V.leaves[R])[lane] = w_c1; }
-  if (lane < DEVSPLIT_WORDS) { reinterpret_cast<int*>(&V.best[leaf])[lane] = w_b0; reinterpret_cast<int*>(&V.best[R])[lane] = w_b1; }
-  if (lane < 4) reinterpret_cast<int*>(&V.leaf_key[leaf])[lane] = w_k;
-  else if (lane < 8) reinterpret_cast<int*>(&V.leaf_key[R])[lane - 4] = w_k;
+  __syncwarp();
+  warp_copy_words(&V.leaves[leaf], &S->child[0], DEVLEAF_WORDS, lane);
+  warp_copy_words(&V.leaves[R], &S->child[1], DEVLEAF_WORDS, lane);
+  warp_copy_words(&V.best[leaf], &S->best[0], DEVSPLIT_WORDS, lane);
+  warp_copy_words(&V.best[R], &S->best[1], DEVSPLIT_WORDS, lane);
+  warp_copy_words(&V.leaf_key[leaf], &S->key[0], 4, lane);
+  warp_copy_words(&V.leaf_key[R], &S->key[1], 4, lane);
   if (lane == 0) { V.expanded[leaf] = 0; V.expanded[R] = 0; }
 }
 
@@ -772,7 +751,7 @@ __device__ void commit_leaf(const DevView& V, int leaf, int lane) {
 }
 
 // warp 0, training: steps 2 and 3 of the control step -- general version, leaf keys re-read from memory every pass
-__device__ __noinline__ void commit_and_select_global(const DevView& V, int lane) {
+__device__ void commit_and_select_global(const DevView& V, int lane) {
   DevCtl* c = V.ctl;
   int nl = c->num_leaves;
   const int max_leaves = V.p.num_leaves;
@@ -809,33 +788,20 @@ __device__ __noinline__ void commit_and_select_global(const DevView& V, int lane
   if (lane == 0) { c->num_items = ni; c->round += 1; }
 }
 
-// Control step, trees of up to 256 leaves -- a parallel formulation of the reference's sequential loop "pick the open
-// leaf with the largest gain; stop if it is not expanded; otherwise commit it and go on" (serial_tree_learner.cpp:
-// 181-199).  Leaf keys are handled as integers: `gk` = order-preserving 64-bit image of the gain (larger = better),
-// `tie` = real feature << 16 | leaf (smaller = better; -1 counts as INT_MAX as in SplitInfo::operator>), so "a beats
-// b" is two integer compares and the order is total.
-//   * the leaves popped by the loop are, in order, the EXPANDED open leaves sorted by key: e_0 > e_1 > ...;
-//   * e_i is committed iff its gain is positive and it beats every NON-expanded open leaf that exists at that moment:
-//     those of the start (their best key = B0) and the children of e_0 .. e_{i-1} (children are never expanded yet);
-//     so with P_i = max(B0, children of e_0..e_{i-1}) (an exclusive prefix maximum over the sorted list) the commits
-//     are the longest prefix with e_i > P_i -- cut short by the leaf budget;
-//   * the loop's end state (done = no positive gain left / tree full) follows from the first element not committed.
-// Sorting by rank counting, the prefix maximum by a block scan: a few hundred cycles instead of one dependent
-// warp-collective pass per commit.
-#define CTRL_MAX_LEAVES 256
+// Control step, trees of up to 256 leaves.  Leaf keys are handled as integers: `gk` = order-preserving 64-bit image
+// of the gain (larger = better), `tie` = real feature << 16 | leaf (smaller = better; -1 counts as INT_MAX as in
+// SplitInfo::operator>), so "a beats b" is two integer compares.
+#define CTRL_SLOTS 8
+#define CTRL_MAX_LEAVES (32 * CTRL_SLOTS)
 struct CtrlShared {
-  unsigned long long gk[CTRL_MAX_LEAVES];    // key of every open leaf (thread l = leaf l); after the commits: final keys
+  SplitKey ck[CTRL_MAX_LEAVES][2];          // children's keys of every expanded leaf (staged by the whole block)
+  unsigned long long gk[CTRL_MAX_LEAVES];    // after the commit loop: final key of every open leaf ...
   unsigned long long tie[CTRL_MAX_LEAVES];
-  int pad[CTRL_MAX_LEAVES];                  // packed split descriptor of the leaf's best split
-  int ex[CTRL_MAX_LEAVES];                   // expanded flag
-  int eligible[CTRL_MAX_LEAVES];             // may be expanded next (open, not expanded, gain > 0)
-  int sleaf[CTRL_MAX_LEAVES];                // expanded leaves sorted by key, best first
-  unsigned long long xk[CTRL_MAX_LEAVES];    // gk of the expanded leaves, 0 for the others (rank loops read one array)
-  unsigned long long ek[CTRL_MAX_LEAVES];    // gk of the eligible leaves, 0 for the others
-  SplitKey ck[CTRL_MAX_LEAVES][2];           // children keys of every leaf's DevSpec (meaningful where expanded)
-  unsigned long long pg[CTRL_MAX_LEAVES + 1], pt[CTRL_MAX_LEAVES + 1];  // P_i (index ne = over all expanded leaves)
-  unsigned long long wg[FS_WARPS], wt[FS_WARPS];
-  int first_bad, nc, done, nl;
+  int pad[CTRL_MAX_LEAVES];                  // ... its packed split descriptor
+  int eligible[CTRL_MAX_LEAVES];             // ... and whether it may be expanded next (open, not expanded, gain > 0)
+  int ex[CTRL_MAX_LEAVES], pos[CTRL_MAX_LEAVES];  // expanded flag, gain > 0
+  int commit[CTRL_MAX_LEAVES];               // leaves to commit, in order
+  int nc, done, nl;
 };
 __device__ __forceinline__ unsigned long long gain_key64(double g) {
   unsigned long long u = (unsigned long long)__double_as_longlong(g);
@@ -844,159 +810,77 @@ __device__ __forceinline__ unsigned long long gain_key64(double g) {
 __device__ __forceinline__ unsigned long long tie_key64(int real_feature, int leaf) {
   return ((unsigned long long)(real_feature == -1 ? 0x7fffffffu : (unsigned)real_feature) << 16) | (unsigned)leaf;
 }
-__device__ __forceinline__ bool key_beats(unsigned long long g1, unsigned long long t1, unsigned long long g2, unsigned long long t2) {
-  return g1 > g2 || (g1 == g2 && t1 < t2);
-}
-__device__ __forceinline__ void key_max(unsigned long long& g, unsigned long long& t, unsigned long long g2, unsigned long long t2) {
-  if (key_beats(g2, t2, g, t)) { g = g2; t = t2; }
-}
-// gain > 0 (NaN and -0.0 are not), read off the key
-__device__ __forceinline__ bool key_positive(unsigned long long g) {
-  return g > 0x8000000000000000ull && g <= 0xFFF0000000000000ull;
-}
-#define KEY_NONE_G 0ull           /* loses against every real key */
-#define KEY_NONE_T (~0ull)
 
-// all FS_THREADS threads: commits, end state and the next round's items.  nl0 / ns0 = leaves / splits so far.
-#ifdef LGBCU_STAGE_TIMERS
-#define QSTAGE(i) do { if (threadIdx.x == 0) { long long t_ = clock64(); g_stage_cycles[16 + (i)] += (unsigned long long)(t_ - tq_); tq_ = t_; } } while (0)
-#else
-#define QSTAGE(i) do {} while (0)
-#endif
-__device__ void control_step(const DevView& V, CtrlShared& C, int nl0, int ns0) {
-  DevCtl* c = V.ctl;
-#ifdef LGBCU_STAGE_TIMERS
-  long long tq_ = clock64();
-#endif
-  const int l = threadIdx.x, lane = l & 31, warp = l >> 5;   // FS_THREADS == CTRL_MAX_LEAVES
-  const int max_leaves = V.p.num_leaves;
-  // ---- keys of the open leaves; children keys of the expanded ones (children: left keeps the id, right = nl0 + rank)
-  unsigned long long myg = KEY_NONE_G, myt = KEY_NONE_T;
-  int myex = 0, mypad = 0;
-  if (l < nl0) {
-    // one round trip: the leaf's key, its expanded flag and (whether or not it is expanded) the keys of its DevSpec
+// all threads: thread l loads the key of leaf l into the shared arrays
+__device__ void ctrl_load_keys(const DevView& V, CtrlShared& C, int nl) {
+  const int l = threadIdx.x;  // FS_THREADS == CTRL_MAX_LEAVES
+  C.gk[l] = 0; C.tie[l] = ~0ull; C.pad[l] = 0; C.ex[l] = 0; C.pos[l] = 0;
+  if (l < nl) {
     const SplitKey key = load_key_cg(&V.leaf_key[l]);
-    myex = __ldcg(&V.expanded[l]);
-    C.ck[l][0] = load_key_cg(&V.spec[l].key[0]); C.ck[l][1] = load_key_cg(&V.spec[l].key[1]);
-    myg = gain_key64(key.gain); myt = tie_key64(key.real_feature, l); mypad = key.pad;
+    C.gk[l] = gain_key64(key.gain); C.tie[l] = tie_key64(key.real_feature, l); C.pad[l] = key.pad; C.pos[l] = key.gain > 0.0;
+    const int ex = __ldcg(&V.expanded[l]);
+    C.ex[l] = ex;
+    if (ex) { C.ck[l][0] = load_key_cg(&V.spec[l].key[0]); C.ck[l][1] = load_key_cg(&V.spec[l].key[1]); }
   }
-  C.gk[l] = myg; C.tie[l] = myt; C.pad[l] = mypad; C.ex[l] = myex; C.xk[l] = myex ? myg : 0ull;
-  if (l == 0) C.first_bad = CTRL_MAX_LEAVES;
-  // ---- B0 = best non-expanded open leaf
-  {
-    unsigned long long g = myex ? KEY_NONE_G : myg, t = myex ? KEY_NONE_T : myt;
-    for (int o = 16; o > 0; o >>= 1) key_max(g, t, __shfl_xor_sync(FULL_MASK, g, o), __shfl_xor_sync(FULL_MASK, t, o));
-    if (lane == 0) { C.wg[warp] = g; C.wt[warp] = t; }
-  }
-  const int ne = __syncthreads_count(myex);   // (also publishes C.gk .. C.ex and the warp maxima)
-  QSTAGE(0);
-  unsigned long long b0g = KEY_NONE_G, b0t = KEY_NONE_T;
+}
+
+// warp 0: step 2 -- which leaves are committed, in the reference's order (ArgMax over best_split_per_leaf_).  The
+// keys live in shared memory (leaf = lane + 32 * slot: conflict-free); a pass is 8 local integer compares and one warp
+// arg-max; a commit overwrites the two entries it changes with the children's keys.
+__device__ void plan_commits(const DevView& V, int lane, CtrlShared& C) {
+  DevCtl* c = V.ctl;
+  const int max_leaves = V.p.num_leaves;
+  int nl = c->num_leaves;
+  int done = 0, nc = 0;
+  while (true) {
+    unsigned long long bg = 0, bt = ~0ull; int bl = -1;
 #pragma unroll
-  for (int w = 0; w < FS_WARPS; ++w) key_max(b0g, b0t, C.wg[w], C.wt[w]);
-  // ---- sort the expanded leaves by key: rank = expanded leaves that beat this one
-  if (myex) {   // (a key is never 0: gain_key64 maps every double above 0x000f...)
-    int rank = 0;
-#pragma unroll 4
-    for (int m = 0; m < nl0; ++m) {
-      const unsigned long long gm = C.xk[m];
-      rank += (gm > myg || (gm == myg && C.tie[m] < myt)) ? 1 : 0;
-    }
-    C.sleaf[rank] = l;
-  }
-  __syncthreads();
-  QSTAGE(1);
-  // ---- thread i = sorted position i: P_i by an exclusive block scan (max) of the children's keys
-  int leaf_i = -1;
-  unsigned long long eg = KEY_NONE_G, et = KEY_NONE_T;           // key of e_i
-  unsigned long long g0 = KEY_NONE_G, t0 = KEY_NONE_T, g1 = KEY_NONE_G, t1 = KEY_NONE_T;  // its children
-  int pad0 = 0, pad1 = 0;
-  if (l < ne) {
-    leaf_i = C.sleaf[l];
-    eg = C.gk[leaf_i]; et = C.tie[leaf_i];
-    const SplitKey c0 = C.ck[leaf_i][0], c1 = C.ck[leaf_i][1];
-    g0 = gain_key64(c0.gain); t0 = tie_key64(c0.real_feature, leaf_i); pad0 = c0.pad;
-    g1 = gain_key64(c1.gain); t1 = tie_key64(c1.real_feature, nl0 + l); pad1 = c1.pad;
-  }
-  {
-    unsigned long long g = g0, t = t0;
-    key_max(g, t, g1, t1);
-#pragma unroll
-    for (int o = 1; o < 32; o <<= 1) {
-      const unsigned long long g2 = __shfl_up_sync(FULL_MASK, g, o), t2 = __shfl_up_sync(FULL_MASK, t, o);
-      if (lane >= o) key_max(g, t, g2, t2);
-    }
-    __syncthreads();   // C.wg / C.wt are reused
-    if (lane == 31) { C.wg[warp] = g; C.wt[warp] = t; }
-    __syncthreads();
-    unsigned long long pg = b0g, pt = b0t;
-    for (int w = 0; w < warp; ++w) key_max(pg, pt, C.wg[w], C.wt[w]);
-    key_max(g, t, pg, pt);                 // inclusive: B0 and the children of e_0 .. e_i
-    C.pg[l + 1] = g; C.pt[l + 1] = t;
-    if (l == 0) { C.pg[0] = b0g; C.pt[0] = b0t; }
-  }
-  __syncthreads();
-  QSTAGE(2);
-  // ---- the commits: longest prefix of e_i with positive gain that beats P_i, within the leaf budget
-  if (l < ne) {
-    const bool ok = key_positive(eg) && key_beats(eg, et, C.pg[l], C.pt[l]) && (nl0 + l < max_leaves);
-    if (!ok) atomicMin(&C.first_bad, l);
-  }
-  __syncthreads();
-  const int nc = min(C.first_bad, ne);
-  const int nl1 = nl0 + nc;
-  int done = 0;
-  if (nc > 0 && nl1 >= max_leaves) done = 2;                       // the tree is full
-  else {
-    unsigned long long ng = C.pg[nc], nt = C.pt[nc];                 // what the loop would pick next
-    if (nc < ne) { const int e = C.sleaf[nc]; key_max(ng, nt, C.gk[e], C.tie[e]); }
-    if (!key_positive(ng)) done = 1;                                 // "No further splits with positive gain"
-  }
-  __syncthreads();   // every thread has read the old keys of the committed leaves
-  // ---- the committed leaves are replaced by their children (not expanded)
-  if (l < nc) {
-    C.gk[leaf_i] = g0; C.tie[leaf_i] = t0; C.pad[leaf_i] = pad0; C.ex[leaf_i] = 0;
-    const int R = nl0 + l;
-    C.gk[R] = g1; C.tie[R] = t1; C.pad[R] = pad1; C.ex[R] = 0;
-  }
-  __syncthreads();
-  const int mine = (l < nl1 && !done && key_positive(C.gk[l]) && C.ex[l] == 0) ? 1 : 0;
-  C.eligible[l] = mine; C.ek[l] = mine ? C.gk[l] : 0ull;
-  if (l == 0) { C.nc = nc; C.done = done; C.nl = nl1; }
-  __syncthreads();
-  QSTAGE(3);
-  // ---- the next round's items = the K eligible leaves with the best keys; a leaf's item index is the number of
-  // eligible leaves that beat it
-  {
-    int K = c->lookahead;
-    if (K > max_leaves - nl1) K = max_leaves - nl1;
-    if (mine) {
-      const unsigned long long g = C.gk[l], t = C.tie[l];
-      int rank = 0;
-#pragma unroll 4
-      for (int m = 0; m < nl1; ++m) {
-        const unsigned long long gm = C.ek[m];
-        rank += (gm > g || (gm == g && C.tie[m] < t)) ? 1 : 0;
-      }
-      if (rank < K) {
-        const int pd = C.pad[l];
-        c->item_leaf[rank] = l;
-        c->item_feature[rank] = pd & ((1 << KEY_FEAT_BITS) - 1);
-        c->item_threshold[rank] = (pd >> KEY_FEAT_BITS) & 511;
-        c->item_default_left[rank] = (pd >> (KEY_FEAT_BITS + 9)) & 1;
+    for (int k = 0; k < CTRL_SLOTS; ++k) {
+      const int l = lane + 32 * k;
+      if (l < nl) {
+        const unsigned long long g = C.gk[l], t = C.tie[l];
+        if (bl < 0 || g > bg || (g == bg && t < bt)) { bg = g; bt = t; bl = l; }
       }
     }
-    const int n_elig = __syncthreads_count(mine);
-    if (l == 0) {
-      c->num_items = n_elig < K ? n_elig : (K > 0 ? K : 0);
-      c->round += 1;
-      if (done) c->done = done;
+    const unsigned ghi = (unsigned)(bg >> 32), glo = (unsigned)bg;
+    bool a = bl >= 0;
+    const unsigned m1 = __reduce_max_sync(FULL_MASK, a ? ghi : 0u);
+    a = a && ghi == m1;
+    unsigned bal = __ballot_sync(FULL_MASK, a);
+    if (bal & (bal - 1)) {
+      const unsigned m2 = __reduce_max_sync(FULL_MASK, a ? glo : 0u);
+      a = a && glo == m2;
+      bal = __ballot_sync(FULL_MASK, a);
+      if (bal & (bal - 1)) {
+        const unsigned m3 = __reduce_min_sync(FULL_MASK, a ? (unsigned)(bt >> 32) : 0xffffffffu);
+        a = a && (unsigned)(bt >> 32) == m3;
+        const unsigned m4 = __reduce_min_sync(FULL_MASK, a ? (unsigned)bt : 0xffffffffu);
+        a = a && (unsigned)bt == m4;
+        bal = __ballot_sync(FULL_MASK, a);
+      }
     }
+    if (bal == 0) { done = 1; break; }
+    bl = __shfl_sync(FULL_MASK, bl, __ffs(bal) - 1);
+    if (!C.pos[bl]) { done = 1; break; }   // "No further splits with positive gain"
+    if (!C.ex[bl]) break;                  // its children are not known yet
+    const int R = nl;
+    if (lane == 0) {
+      C.commit[nc] = bl;
+      const SplitKey k0 = C.ck[bl][0], k1 = C.ck[bl][1];
+      C.gk[bl] = gain_key64(k0.gain); C.tie[bl] = tie_key64(k0.real_feature, bl); C.pad[bl] = k0.pad; C.pos[bl] = k0.gain > 0.0; C.ex[bl] = 0;
+      C.gk[R] = gain_key64(k1.gain); C.tie[R] = tie_key64(k1.real_feature, R); C.pad[R] = k1.pad; C.pos[R] = k1.gain > 0.0; C.ex[R] = 0;
+    }
+    __syncwarp();
+    ++nc;
+    nl += 1;
+    if (nl >= max_leaves) { done = 2; break; }  // the tree is full
   }
-  QSTAGE(4);
-  // ---- the committed children enter the leaf table, the split records are written
-  for (int i = warp; i < nc; i += FS_WARPS) commit_leaf_as(V, C.sleaf[i], nl0 + i, ns0 + i, lane);
-  QSTAGE(5);
-  if (l == 0) { c->num_leaves = nl1; c->num_splits = ns0 + nc; }
+#pragma unroll
+  for (int k = 0; k < CTRL_SLOTS; ++k) {
+    const int l = lane + 32 * k;
+    C.eligible[l] = (l < nl && !done && C.pos[l] && C.ex[l] == 0) ? 1 : 0;
+  }
+  if (lane == 0) { C.nc = nc; C.done = done; C.nl = nl; }
 }
 
 // mode 0: training.  grid = (num_features, 2 * LGB_KMAX): blockIdx.y = 2 * item + sel; sel 0 scans the smaller child of
@@ -1037,41 +921,8 @@ __global__ void __launch_bounds__(FS_THREADS, 4) k_find_split(DevView V, int mod
   STAGE(0);
   if (active) find_item(V, S, f, sel, T);
   STAGE(4);
-  // ---- the last block of a ROW of the grid (one scanned leaf) reduces that leaf's per-feature candidates
-  // (SplitInfo::operator>) and stores its best split -- into the leaf table (root / step-wise) or the DevSpec of the
-  // leaf being expanded -- while other rows are still being scanned
-  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
-  const bool row_active = (mode == 1 || root_round) ? (y == 0) : (e < ni);
   __threadfence();
   __syncthreads();
-  if (row_active) {
-    if (threadIdx.x == 0) s_last = (atomicAdd(&c->row_done[y], 1u) == gridDim.x - 1);
-    __syncthreads();
-    if (s_last) {
-      if (warp == 0) {
-        if (mode == 1 || root_round) {
-          const int leaf = mode == 1 ? leaf_arg : 0;
-          if (mode == 1 || !c->skip_find) {
-            const PairBest b = warp_reduce_feature_keys(V, 0, lane);
-            store_leaf_best(V, 0, b, &V.best[leaf], &V.leaf_key[leaf], lane);
-          }
-        } else {
-          DevSpec* sp = &V.spec[c->item_leaf[e]];
-          const int child = sel == 0 ? sp->smaller : 1 - sp->smaller;   // row 2e = the smaller child, 2e + 1 = the larger
-          if (sp->skip_find) {
-            store_none_split(&sp->best[child], lane);
-            if (lane == 0) store_key(&sp->key[child], none_key());
-          } else {
-            const PairBest b = warp_reduce_feature_keys(V, y, lane);
-            store_leaf_best(V, y, b, &sp->best[child], &sp->key[child], lane);
-          }
-        }
-        if (lane == 0) c->row_done[y] = 0;
-      }
-      __threadfence();
-    }
-    __syncthreads();
-  }
   if (threadIdx.x == 0) {
     const unsigned ticket = atomicAdd(&c->feat_done, 1u);
     s_last = (ticket == gridDim.x * gridDim.y - 1);
@@ -1079,12 +930,41 @@ __global__ void __launch_bounds__(FS_THREADS, 4) k_find_split(DevView V, int mod
   __syncthreads();
   STAGE(5);
   if (!s_last) return;
-  // ---- control step, last block of the grid only
+  // ---- control step, last block only.  Step 1: every warp reduces feat_key rows (one leaf each) and stores that
+  // leaf's best split where it belongs.
   __shared__ CtrlShared C;
+  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
 #ifdef LGBCU_STAGE_TIMERS
   long long tc0 = clock64();
+  long long tq_ = tc0;
+#define QSTAGE(i) do { if (threadIdx.x == 0) { long long t_ = clock64(); g_stage_cycles[16 + (i)] += (unsigned long long)(t_ - tq_); tq_ = t_; } } while (0)
+#else
+#define QSTAGE(i) do {} while (0)
 #endif
   if (threadIdx.x == 0) c->feat_done = 0;
+  if (mode == 1 || root_round) {
+    const int leaf = mode == 1 ? leaf_arg : 0;
+    if (warp == 0 && (mode == 1 || !c->skip_find)) {
+      const PairBest b = warp_reduce_feature_keys(V, 0, lane);
+      store_leaf_best(V, 0, b, &V.best[leaf], &V.leaf_key[leaf], lane);
+    }
+  } else {
+    for (int p = warp; p < 2 * ni; p += FS_WARPS) {
+      const int i = p >> 1, which = p & 1;  // which = 0: the smaller child's row, 1: the larger child's
+      DevSpec* sp = &V.spec[c->item_leaf[i]];
+      const int child = which == 0 ? sp->smaller : 1 - sp->smaller;
+      if (sp->skip_find) {
+        store_none_split(&sp->best[child], lane);
+        if (lane == 0) store_key(&sp->key[child], none_key());
+      } else {
+        const PairBest b = warp_reduce_feature_keys(V, p, lane);
+        store_leaf_best(V, p, b, &sp->best[child], &sp->key[child], lane);
+      }
+    }
+  }
+  __threadfence_block();
+  __syncthreads();
+  QSTAGE(0);
   if (mode == 1) return;
   if (!root_round && threadIdx.x < ni) V.expanded[c->item_leaf[threadIdx.x]] = 1;
   __threadfence_block();
@@ -1094,7 +974,48 @@ __global__ void __launch_bounds__(FS_THREADS, 4) k_find_split(DevView V, int mod
     if (warp == 0) commit_and_select_global(V, lane);
     return;
   }
-  control_step(V, C, nl0, ns0);
+  // step 2: stage every open leaf's key (and the children's keys of the expanded ones), let warp 0 decide the commits
+  ctrl_load_keys(V, C, nl0);
+  __syncthreads();
+  QSTAGE(1);
+  if (warp == 0) plan_commits(V, lane, C);
+  __syncthreads();
+  QSTAGE(2);
+  // step 3, all threads: the next round's items = the K eligible leaves with the best keys; a leaf's item index is the
+  // number of eligible leaves that beat it
+  {
+    int K = c->lookahead;
+    if (K > V.p.num_leaves - C.nl) K = V.p.num_leaves - C.nl;
+    const int l = threadIdx.x;  // FS_THREADS == CTRL_MAX_LEAVES
+    const int mine = C.eligible[l];
+    int rank = 0;
+    if (mine) {
+      const unsigned long long g = C.gk[l], t = C.tie[l];
+      const int nlf = C.nl;
+      for (int m = 0; m < nlf; ++m) {
+        const unsigned long long gm = C.gk[m], tm = C.tie[m];
+        rank += (C.eligible[m] && (gm > g || (gm == g && tm < t))) ? 1 : 0;
+      }
+      if (rank < K) {
+        const int pd = C.pad[l];
+        c->item_leaf[rank] = l;
+        c->item_feature[rank] = pd & ((1 << KEY_FEAT_BITS) - 1);
+        c->item_threshold[rank] = (pd >> KEY_FEAT_BITS) & 511;
+        c->item_default_left[rank] = (pd >> (KEY_FEAT_BITS + 9)) & 1;
+      }
+    }
+    const int n_elig = __syncthreads_count(mine);
+    if (threadIdx.x == 0) {
+      c->num_items = n_elig < K ? n_elig : (K > 0 ? K : 0);
+      c->round += 1;
+      if (C.done) c->done = C.done;
+    }
+  }
+  QSTAGE(3);
+  const int nc = C.nc;
+  for (int i = warp; i < nc; i += FS_WARPS) commit_leaf_as(V, C.commit[i], nl0 + i, ns0 + i, lane);
+  QSTAGE(4);
+  if (threadIdx.x == 0) { c->num_leaves = nl0 + nc; c->num_splits = ns0 + nc; }
 #ifdef LGBCU_STAGE_TIMERS
   if (threadIdx.x == 0) { g_stage_cycles[6] += (unsigned long long)(clock64() - tc0); g_stage_cycles[7] += 1; }
 #endif

@@ -52,14 +52,13 @@ int lgbcu_valid_create(LgbCuContext* c, int32_t num_data, const uint8_t* bins, i
   v.n = num_data;
   CU(dev_alloc(&v.d_bins, (size_t)num_data * c->stride));
   {
-    uint8_t* packed = nullptr;
-    CU(dev_alloc(&packed, (size_t)num_data * c->F));
-    CU(cudaMemcpyAsync(packed, bins, (size_t)num_data * c->F, cudaMemcpyHostToDevice, c->stream));
+    struct Tmp { uint8_t* p = nullptr; ~Tmp() { if (p) cudaFree(p); } } packed;   // released on every way out
+    CU(dev_alloc(&packed.p, (size_t)num_data * c->F));
+    CU(cudaMemcpyAsync(packed.p, bins, (size_t)num_data * c->F, cudaMemcpyHostToDevice, c->stream));
     LAUNCH(k_pad_rows, grid_for(c, (long long)num_data * (c->stride / 4), 256), 256, 0, c->stream, (long long)num_data,
-           c->F, c->stride, packed, v.d_bins);
+           c->F, c->stride, packed.p, v.d_bins);
     CU(cudaGetLastError());
     CU(cudaStreamSynchronize(c->stream));
-    cudaFree(packed);
   }
   CU(dev_alloc(&v.d_score, (size_t)num_data));
   CU(cudaMemsetAsync(v.d_score, 0, sizeof(double) * num_data, c->stream));

@@ -52,7 +52,7 @@ int LGBM_DatasetCreateFromMat(const void* data, int data_type, int32_t nrow, int
     *out = Dataset::FromDenseMatrix(data, data_type, nrow, ncol, is_row_major != 0, config);
   } else {
     *out = Dataset::FromDenseMatrixAligned(data, data_type, nrow, ncol, is_row_major != 0,
-                                           *reinterpret_cast<const Dataset*>(reference));
+                                           *reinterpret_cast<const Dataset*>(reference), config);
   }
   API_END();
 }

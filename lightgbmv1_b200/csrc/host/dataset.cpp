@@ -3,6 +3,7 @@
 #include <omp.h>
 
 #include <algorithm>
+#include <cstdlib>
 #include <cstring>
 
 #include "lgbcu.h"
@@ -209,12 +210,12 @@ Dataset* Dataset::FromDenseMatrix(const void* data, int data_type, int32_t nrow,
     ds->mappers_.push_back(all[f]);
   }
   for (int c = 0; c < ncol; ++c) ds->feature_names_.push_back("Column_" + std::to_string(c));
-  ds->BinAllRows(data, data_type, nrow, ncol, row_major);
+  ds->BinAllRows(data, data_type, nrow, ncol, row_major, config.gpu_device_id);
   return ds.release();
 }
 
 Dataset* Dataset::FromDenseMatrixAligned(const void* data, int data_type, int32_t nrow, int32_t ncol, bool row_major,
-                                         const Dataset& ref) {
+                                         const Dataset& ref, const Config& config) {
   if (ncol != ref.num_total_features_) Log::Fatal("The number of features in data (%d) is not the same as it was in training data (%d).", ncol, ref.num_total_features_);
   std::unique_ptr<Dataset> ds(new Dataset(nrow));
   ds->num_total_features_ = ncol;
@@ -222,7 +223,7 @@ Dataset* Dataset::FromDenseMatrixAligned(const void* data, int data_type, int32_
   ds->inner_to_real_ = ref.inner_to_real_;
   ds->real_to_inner_ = ref.real_to_inner_;
   ds->feature_names_ = ref.feature_names_;
-  ds->BinAllRows(data, data_type, nrow, ncol, row_major);
+  ds->BinAllRows(data, data_type, nrow, ncol, row_major, config.gpu_device_id);
   return ds.release();
 }
 
@@ -234,9 +235,36 @@ uint32_t Dataset::stored_value(int inner, double v) const {
   return bin + 1;
 }
 
-void Dataset::BinAllRows(const void* data, int data_type, int32_t nrow, int32_t ncol, bool row_major) {
-  const MatView M{data, data_type, nrow, ncol, row_major};
+// The row push loop of LGBM_DatasetCreateFromMat (src/c_api.cpp:1082-1097).  With a CUDA device the N x F map runs
+// there (lgbcu_bin_matrix: the reference's ValueToBin search per element, bit-identical) and the binned matrix stays
+// in HBM for the learner to adopt; the host copy is fetched only if somebody asks for it (bins()).  Without any
+// device a Dataset can still be built -- the same map on the host threads -- but nothing can be trained with it:
+// LGBM_BoosterCreate fails ("no CUDA device available").  LGBM_B200_HOST_BINNING=1 forces the host loop (tests
+// compare the two).
+void Dataset::BinAllRows(const void* data, int data_type, int32_t nrow, int32_t ncol, bool row_major, int device) {
   const int F = num_features();
+  int ndev = 0;
+  lgbcu_device_count(&ndev);
+  const char* force_host = std::getenv("LGBM_B200_HOST_BINNING");
+  if (ndev > 0 && F > 0 && !(force_host && std::atoi(force_host) != 0)) {
+    std::vector<LgbCuBinFeature> feats(F);
+    std::vector<double> bounds;
+    for (int f = 0; f < F; ++f) {
+      const BinMapper& m = *mappers_[f];
+      feats[f].column = inner_to_real_[f]; feats[f].num_bin = m.num_bin();
+      feats[f].most_freq_bin = static_cast<int>(m.most_freq_bin()); feats[f].missing_type = m.missing_type();
+      feats[f].bound_offset = static_cast<int>(bounds.size()); feats[f].reserved = 0;
+      bounds.insert(bounds.end(), m.upper_bounds().begin(), m.upper_bounds().end());
+    }
+    int dev = device >= 0 ? device : 0;
+    if (dev >= ndev) Log::Fatal("gpu_device_id %d out of range (have %d devices)", dev, ndev);
+    if (lgbcu_bin_matrix(dev, data, data_type, nrow, ncol, row_major ? 1 : 0, F, feats.data(), bounds.data(),
+                         static_cast<int>(bounds.size()), &dev_bins_) != 0) {
+      Log::Fatal("%s", lgbcu_last_error());
+    }
+    return;
+  }
+  const MatView M{data, data_type, nrow, ncol, row_major};
   bins_.assign(static_cast<size_t>(nrow) * std::max(F, 1), 0);
 #pragma omp parallel for schedule(static)
   for (int32_t r = 0; r < nrow; ++r) {
@@ -247,9 +275,18 @@ void Dataset::BinAllRows(const void* data, int data_type, int32_t nrow, int32_t 
   bins_pinned_ = lgbcu_pin_host_buffer(bins_.data(), bins_.size()) == 0;
 }
 
+const std::vector<uint8_t>& Dataset::bins() const {
+  if (bins_.empty() && dev_bins_ != nullptr) {
+    bins_.assign(static_cast<size_t>(num_data_) * std::max(num_features(), 1), 0);
+    if (lgbcu_binned_copy_to_host(dev_bins_, bins_.data()) != 0) Log::Fatal("%s", lgbcu_last_error());
+  }
+  return bins_;
+}
+
 Dataset::~Dataset() {
   if (label_pinned_) lgbcu_unpin_host_buffer(meta_.label.data());
   if (bins_pinned_) lgbcu_unpin_host_buffer(bins_.data());
+  if (dev_bins_) lgbcu_binned_free(dev_bins_);
 }
 
 uint64_t Dataset::num_total_bin() const {

@@ -10,6 +10,7 @@
 
 #include "bin_mapper.h"
 #include "config.h"
+#include "lgbcu.h"
 
 namespace lgb {
 
@@ -27,7 +28,7 @@ class Dataset {
                                   const Config& config);
   // ... with a reference dataset: reuse its mappers and feature order (Dataset::CreateValid)
   static Dataset* FromDenseMatrixAligned(const void* data, int data_type, int32_t nrow, int32_t ncol, bool row_major,
-                                         const Dataset& reference);
+                                         const Dataset& reference, const Config& config);
 
   ~Dataset();
   Dataset(const Dataset&) = delete;
@@ -39,7 +40,10 @@ class Dataset {
   int real_feature_index(int inner) const { return inner_to_real_[inner]; }
   int inner_feature_index(int real) const { return real_to_inner_[real]; }
   const BinMapper& mapper(int inner) const { return *mappers_[inner]; }
-  const std::vector<uint8_t>& bins() const { return bins_; }  // row-major [num_data][num_features]
+  // row-major [num_data][num_features] stored values on the HOST.  When the matrix was binned on the device it is
+  // fetched on first use (validation sets, dumps); training adopts the device copy directly (device_bins()).
+  const std::vector<uint8_t>& bins() const;
+  LgbCuBinnedMatrix* device_bins() const { return dev_bins_; }
   uint64_t num_total_bin() const;
   Metadata& metadata() { return meta_; }
   const Metadata& metadata() const { return meta_; }
@@ -54,14 +58,15 @@ class Dataset {
 
  private:
   explicit Dataset(data_size_t n) : num_data_(n) {}
-  void BinAllRows(const void* data, int data_type, int32_t nrow, int32_t ncol, bool row_major);
+  void BinAllRows(const void* data, int data_type, int32_t nrow, int32_t ncol, bool row_major, int device);
 
   data_size_t num_data_;
   int num_total_features_ = 0;
   std::vector<std::shared_ptr<BinMapper>> mappers_;  // per inner feature
   std::vector<int> inner_to_real_, real_to_inner_;
-  std::vector<uint8_t> bins_;
-  bool bins_pinned_ = false;  // page-locked for the upload (lgbcu_pin_host_buffer)
+  mutable std::vector<uint8_t> bins_;
+  mutable bool bins_pinned_ = false;  // page-locked for the upload (lgbcu_pin_host_buffer)
+  LgbCuBinnedMatrix* dev_bins_ = nullptr;  // the matrix as binned on the device (lgbcu_bin_matrix), if it was
   bool label_pinned_ = false;
   std::vector<std::string> feature_names_;
   Metadata meta_;

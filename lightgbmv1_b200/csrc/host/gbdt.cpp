@@ -66,7 +66,14 @@ GBDT::GBDT(const Dataset* train, const Config& config)
   }
   if (!config_.feature_contri.empty() && static_cast<int>(config_.feature_contri.size()) != train_->num_total_features())
     Log::Fatal("Check failed: feature_contri size");
-  Check(lgbcu_set_dataset(ctx_, N, F, train_->bins().data(), meta.data()));
+  {
+    // the matrix is usually already in HBM (binned there by LGBM_DatasetCreateFromMat): adopt it without a host trip
+    LgbCuBinnedMatrix* dm = train_->device_bins();
+    int dm_dev = -1;
+    if (dm) lgbcu_binned_device(dm, &dm_dev);
+    if (dm && dm_dev == dev) Check(lgbcu_set_dataset_binned(ctx_, dm, meta.data()));
+    else Check(lgbcu_set_dataset(ctx_, N, F, train_->bins().data(), meta.data()));
+  }
   st.tick("lgbcu_set_dataset");
   LgbCuTreeParams tp;
   tp.num_leaves = config_.num_leaves; tp.max_depth = config_.max_depth; tp.min_data_in_leaf = config_.min_data_in_leaf;

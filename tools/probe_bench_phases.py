@@ -27,7 +27,7 @@ if hasattr(lib, "lgbcu_debug_stages"):   # debug build (tools/build_dbg.sh): blo
     us = lambda i: round(out[i] / 1.965e3 / r, 2)
     print("per round, block 0 (us): find [ctl, load+fix, -, chains+scans, gains, ticket, control]:", [us(i) for i in range(7)],
           " partition [ctl+leaf, flags, barrier, prefix, scatter]:", [us(8 + i) for i in range(5)],
-          " control [load keys+B0, sort expanded, prefix max, commits+table, select items, copies]:", [us(16 + i) for i in range(6)])
+          " control [reduce+store, stage keys, plan, select, copies]:", [us(16 + i) for i in range(5)])
 if hasattr(lib, "lgbcu_debug_hist_stages"):
     o8 = (C.c_ulonglong * 8)()
     lib.lgbcu_debug_hist_stages(o8, 1)

@@ -22,7 +22,7 @@ X, y, ref_rows = G.dp_case(sorted_shards=args.sorted_shards)
 n = len(y)
 ours = capi.ours(); lib = ours.lib
 base = G.BASE + (" " + args.extra if args.extra else "")
-ref_ds = ours.dataset_from_mat(np.ascontiguousarray(X[ref_rows]), base)
+ref_ds = ours.dataset_from_mat(np.ascontiguousarray(X[ref_rows]), base + f" gpu_device_id={local}")
 if world > 1:
     import torch, torch.distributed as dist
     torch.cuda.set_device(local)
