@@ -34,6 +34,8 @@ typedef void* BoosterHandle; /* c_api.h:24 */
 
 /* c_api.h:47 */
 LGBM_B200_API const char* LGBM_GetLastError(void);
+/* c_api.h:54  log lines go to the callback instead of stdout (thread-local, like the reference's Log) */
+LGBM_B200_API int LGBM_RegisterLogCallback(void (*callback)(const char*));
 
 /* c_api.h:229-236  (src/c_api.cpp:998-1015 -> :1018-1100) */
 LGBM_B200_API int LGBM_DatasetCreateFromMat(const void* data, int data_type, int32_t nrow, int32_t ncol, int is_row_major,
@@ -88,6 +90,40 @@ LGBM_B200_API int LGBM_BoosterSaveModelToString(BoosterHandle handle, int start_
 /* c_api.h:1155-1159 */
 LGBM_B200_API int LGBM_BoosterSaveModel(BoosterHandle handle, int start_iteration, int num_iteration,
                                         int feature_importance_type, const char* filename);
+
+/* ---- what python-package/lightgbm/basic.py and engine.py reach around lgb.train on a numpy matrix ----------------- */
+/* c_api.h:283-285 */
+LGBM_B200_API int LGBM_DatasetSetFeatureNames(DatasetHandle handle, const char** feature_names, int num_feature_names);
+/* c_api.h:299-304 */
+LGBM_B200_API int LGBM_DatasetGetFeatureNames(DatasetHandle handle, const int len, int* num_feature_names,
+                                              const size_t buffer_len, size_t* out_buffer_len, char** feature_names);
+/* c_api.h:359-363  label | weight (float32), init_score (float64), group (int32 query boundaries) */
+LGBM_B200_API int LGBM_DatasetGetField(DatasetHandle handle, const char* field_name, int* out_len, const void** out_ptr,
+                                       int* out_type);
+/* c_api.h:371-372  refuses changes of the Dataset-construction parameters (src/c_api.cpp:1441-1451) */
+LGBM_B200_API int LGBM_DatasetUpdateParamChecking(const char* old_parameters, const char* new_parameters);
+/* c_api.h:432-434, 421-423  a booster read back from model text: predicts and saves, cannot train */
+LGBM_B200_API int LGBM_BoosterLoadModelFromString(const char* model_str, int* out_num_iterations, BoosterHandle* out);
+LGBM_B200_API int LGBM_BoosterCreateFromModelfile(const char* filename, int* out_num_iterations, BoosterHandle* out);
+/* c_api.h:487-488  learning rate and tree-growing parameters */
+LGBM_B200_API int LGBM_BoosterResetParameter(BoosterHandle handle, const char* parameters);
+/* c_api.h:540  (GBDT::RollbackOneIter, src/boosting/gbdt.cpp:421-444) */
+LGBM_B200_API int LGBM_BoosterRollbackOneIter(BoosterHandle handle);
+/* c_api.h:622-623, 609-614 */
+LGBM_B200_API int LGBM_BoosterGetNumFeature(BoosterHandle handle, int* out_len);
+LGBM_B200_API int LGBM_BoosterGetFeatureNames(BoosterHandle handle, const int len, int* out_len, const size_t buffer_len,
+                                              size_t* out_buffer_len, char** out_strs);
+/* c_api.h:1235-1238  importance_type 0 = split counts, 1 = total gains */
+LGBM_B200_API int LGBM_BoosterFeatureImportance(BoosterHandle handle, int num_iteration, int importance_type,
+                                                double* out_results);
+/* c_api.h:707-712 */
+LGBM_B200_API int LGBM_BoosterCalcNumPredict(BoosterHandle handle, int num_row, int predict_type, int start_iteration,
+                                             int num_iteration, int64_t* out_len);
+/* c_api.h:1266-1269, 1285-1288  the socket / external-collective linkers: with num_machines > 1 these fail with a message
+ * that points at LGBM_NetworkInitNCCL (below); with num_machines <= 1 they are no-ops, as in the reference */
+LGBM_B200_API int LGBM_NetworkInit(const char* machines, int local_listen_port, int listen_time_out, int num_machines);
+LGBM_B200_API int LGBM_NetworkInitWithFunctions(int num_machines, int rank, void* reduce_scatter_ext_fun,
+                                                void* allgather_ext_fun);
 
 /* Data-parallel rendezvous inside one NVLink box.  Replaces LGBM_NetworkInit (c_api.h:1266-1269: machine list +
  * TCP ports) for tree_learner=data: the ranks share a 128-byte NCCL id instead of a socket mesh.  Rank 0 calls

@@ -5,7 +5,9 @@
 #include <omp.h>
 
 #include <cstring>
+#include <cmath>
 #include <fstream>
+#include <sstream>
 #include <memory>
 #include <mutex>
 
@@ -22,10 +24,73 @@ thread_local char g_last_error[512] = "Everything is fine";
 
 void SetLastError(const char* msg) { std::snprintf(g_last_error, sizeof(g_last_error), "%s", msg); }
 
+// A model read back from its text (LGBM_BoosterLoadModelFromString / CreateFromModelfile, GBDT::LoadModelFromString,
+// src/boosting/gbdt_model_text.cpp:399-560): trees + header, good for prediction and for writing the text again.
+struct LoadedModel {
+  std::string text;
+  std::vector<std::unique_ptr<Tree>> trees;
+  std::vector<std::string> feature_names;
+  int max_feature_idx = -1;
+  std::string objective;   // the header's objective line, e.g. "binary sigmoid:1"
+  double sigmoid = 0.0;    // > 0: predictions are 1 / (1 + exp(-sigmoid * raw))
+};
+
 struct Booster {
   std::unique_ptr<GBDT> gbdt;
+  std::unique_ptr<LoadedModel> loaded;
   std::mutex mu;  // training calls are serialised (the reference holds a writer lock, src/c_api.cpp:346-349)
 };
+
+GBDT* Trainer(BoosterHandle handle) {
+  Booster* b = reinterpret_cast<Booster*>(handle);
+  if (!b || !b->gbdt) Log::Fatal("this booster was loaded from a model string: it can predict and be saved, not trained");
+  return b->gbdt.get();
+}
+
+LoadedModel* ParseModel(const std::string& text) {
+  std::unique_ptr<LoadedModel> m(new LoadedModel());
+  m->text = text;
+  size_t pos = 0;
+  auto next_line = [&](std::string* line) {
+    if (pos >= text.size()) return false;
+    size_t e = text.find('\n', pos);
+    if (e == std::string::npos) e = text.size();
+    *line = text.substr(pos, e - pos);
+    pos = e + 1;
+    return true;
+  };
+  std::string line;
+  bool in_header = true;
+  while (in_header && next_line(&line)) {
+    if (line.rfind("Tree=", 0) == 0) { pos -= line.size() + 1; break; }
+    const size_t eq = line.find('=');
+    if (eq == std::string::npos) continue;
+    const std::string k = line.substr(0, eq), v = line.substr(eq + 1);
+    if (k == "max_feature_idx") m->max_feature_idx = std::atoi(v.c_str());
+    else if (k == "objective") m->objective = v;
+    else if (k == "feature_names") m->feature_names = SplitAny(v, " ");
+    else if (k == "num_class" && std::atoi(v.c_str()) != 1) Log::Fatal("multiclass models are outside this library's path");
+  }
+  if (m->max_feature_idx < 0) Log::Fatal("Model file doesn't specify max_feature_idx");
+  if (m->objective.rfind("binary", 0) == 0) {
+    m->sigmoid = 1.0;
+    const size_t p = m->objective.find("sigmoid:");
+    if (p != std::string::npos) m->sigmoid = std::strtod(m->objective.c_str() + p + 8, nullptr);
+  }
+  // trees: "Tree=i" ... blank line, until "end of trees"
+  std::string cur;
+  bool in_tree = false;
+  while (next_line(&line)) {
+    if (line.rfind("end of trees", 0) == 0) break;
+    if (line.rfind("Tree=", 0) == 0) { in_tree = true; cur.clear(); continue; }
+    if (in_tree) {
+      if (line.empty()) { m->trees.emplace_back(Tree::FromString(cur)); in_tree = false; }
+      else { cur += line; cur += '\n'; }
+    }
+  }
+  if (in_tree && !cur.empty()) m->trees.emplace_back(Tree::FromString(cur));
+  return m.release();
+}
 
 }  // namespace
 
@@ -40,6 +105,12 @@ struct Booster {
 extern "C" {
 
 const char* LGBM_GetLastError(void) { return g_last_error; }
+
+int LGBM_RegisterLogCallback(void (*callback)(const char*)) {
+  API_BEGIN();
+  Log::callback() = callback;
+  API_END();
+}
 
 int LGBM_DatasetCreateFromMat(const void* data, int data_type, int32_t nrow, int32_t ncol, int is_row_major,
                               const char* parameters, const DatasetHandle reference, DatasetHandle* out) {
@@ -109,6 +180,7 @@ int LGBM_BoosterFree(BoosterHandle handle) {
 int LGBM_BoosterUpdateOneIter(BoosterHandle handle, int* is_finished) {
   API_BEGIN();
   Booster* b = reinterpret_cast<Booster*>(handle);
+  Trainer(handle);
   std::lock_guard<std::mutex> lock(b->mu);
   *is_finished = b->gbdt->TrainOneIter(nullptr, nullptr) ? 1 : 0;
   API_END();
@@ -125,7 +197,8 @@ int LGBM_BoosterUpdateOneIterCustom(BoosterHandle handle, const float* grad, con
 
 int LGBM_BoosterGetCurrentIteration(BoosterHandle handle, int* out_iteration) {
   API_BEGIN();
-  *out_iteration = reinterpret_cast<Booster*>(handle)->gbdt->current_iteration();
+  Booster* b = reinterpret_cast<Booster*>(handle);
+  *out_iteration = b->loaded ? static_cast<int>(b->loaded->trees.size()) : b->gbdt->current_iteration();
   API_END();
 }
 
@@ -138,7 +211,8 @@ int LGBM_BoosterNumModelPerIteration(BoosterHandle handle, int* out_tree_per_ite
 
 int LGBM_BoosterNumberOfTotalModel(BoosterHandle handle, int* out_models) {
   API_BEGIN();
-  *out_models = reinterpret_cast<Booster*>(handle)->gbdt->current_iteration();
+  Booster* b = reinterpret_cast<Booster*>(handle);
+  *out_models = b->loaded ? static_cast<int>(b->loaded->trees.size()) : b->gbdt->current_iteration();
   API_END();
 }
 
@@ -183,14 +257,16 @@ int LGBM_BoosterAddValidData(BoosterHandle handle, const DatasetHandle valid_dat
 
 int LGBM_BoosterGetEvalCounts(BoosterHandle handle, int* out_len) {
   API_BEGIN();
-  *out_len = static_cast<int>(reinterpret_cast<Booster*>(handle)->gbdt->EvalNames().size());
+  Booster* b = reinterpret_cast<Booster*>(handle);
+  *out_len = b->loaded ? 0 : static_cast<int>(b->gbdt->EvalNames().size());
   API_END();
 }
 
 int LGBM_BoosterGetEvalNames(BoosterHandle handle, const int len, int* out_len, const size_t buffer_len,
                              size_t* out_buffer_len, char** out_strs) {
   API_BEGIN();
-  const std::vector<std::string> names = reinterpret_cast<Booster*>(handle)->gbdt->EvalNames();
+  Booster* bb = reinterpret_cast<Booster*>(handle);
+  const std::vector<std::string> names = bb->loaded ? std::vector<std::string>() : bb->gbdt->EvalNames();
   *out_buffer_len = 0;
   int idx = 0;
   for (const std::string& name : names) {  // Booster::GetEvalNames (src/c_api.cpp:764-780)
@@ -224,6 +300,31 @@ int LGBM_BoosterPredictForMat(BoosterHandle handle, const void* data, int data_t
   if (predict_type != C_API_PREDICT_NORMAL && predict_type != C_API_PREDICT_RAW_SCORE)
     Log::Fatal("predict_type %d is outside this library's path (normal, raw score)", predict_type);
   Booster* b = reinterpret_cast<Booster*>(handle);
+  if (b->loaded) {
+    const LoadedModel& m = *b->loaded;
+    if (ncol != m.max_feature_idx + 1)
+      Log::Fatal("The number of features in data (%d) is not the same as it was in training data (%d).", ncol, m.max_feature_idx + 1);
+    int n_models = static_cast<int>(m.trees.size());
+    if (num_iteration > 0) n_models = std::min(n_models, num_iteration);
+    const bool raw = predict_type == C_API_PREDICT_RAW_SCORE;
+#pragma omp parallel
+    {
+      std::vector<double> row(ncol);
+#pragma omp for schedule(static)
+      for (int32_t r = 0; r < nrow; ++r) {
+        for (int c = 0; c < ncol; ++c) {
+          const size_t i = is_row_major ? static_cast<size_t>(r) * ncol + c : static_cast<size_t>(c) * nrow + r;
+          row[c] = data_type == 0 ? static_cast<double>(static_cast<const float*>(data)[i]) : static_cast<const double*>(data)[i];
+        }
+        double sc = 0.0;
+        for (int t = 0; t < n_models; ++t) sc += m.trees[t]->Predict(row.data());
+        if (!raw && m.sigmoid > 0) sc = 1.0f / (1.0f + std::exp(-m.sigmoid * sc));
+        out_result[r] = sc;
+      }
+    }
+    *out_len = nrow;
+    return 0;
+  }
   b->gbdt->PredictMat(data, data_type, nrow, ncol, is_row_major != 0, predict_type == C_API_PREDICT_RAW_SCORE,
                       num_iteration, out_result);
   *out_len = nrow;
@@ -234,7 +335,9 @@ int LGBM_BoosterSaveModelToString(BoosterHandle handle, int start_iteration, int
                                   int64_t buffer_len, int64_t* out_len, char* out_str) {
   API_BEGIN();
   (void)feature_importance_type;
-  const std::string model = reinterpret_cast<Booster*>(handle)->gbdt->SaveModelToString(start_iteration, num_iteration);
+  Booster* b = reinterpret_cast<Booster*>(handle);
+  if (b->loaded && !(start_iteration <= 0 && num_iteration <= 0)) Log::Fatal("a loaded model is written back whole (start_iteration / num_iteration not supported)");
+  const std::string model = b->loaded ? b->loaded->text : b->gbdt->SaveModelToString(start_iteration, num_iteration);
   *out_len = static_cast<int64_t>(model.size()) + 1;
   if (*out_len <= buffer_len) std::memcpy(out_str, model.c_str(), *out_len);
   API_END();
@@ -244,10 +347,194 @@ int LGBM_BoosterSaveModel(BoosterHandle handle, int start_iteration, int num_ite
                           const char* filename) {
   API_BEGIN();
   (void)feature_importance_type;
-  const std::string model = reinterpret_cast<Booster*>(handle)->gbdt->SaveModelToString(start_iteration, num_iteration);
+  Booster* b = reinterpret_cast<Booster*>(handle);
+  const std::string model = b->loaded ? b->loaded->text : b->gbdt->SaveModelToString(start_iteration, num_iteration);
   std::ofstream f(filename, std::ios::binary);
   if (!f) Log::Fatal("Model file %s is not available for writes", filename);
   f.write(model.data(), static_cast<std::streamsize>(model.size()));
+  API_END();
+}
+
+// ---- entry points the reference's python package reaches around lgb.train (python-package/lightgbm/basic.py) ------
+
+static void CopyNames(const std::vector<std::string>& names, const int len, int* out_len, const size_t buffer_len,
+                      size_t* out_buffer_len, char** out_strs) {
+  *out_buffer_len = 0;
+  int idx = 0;
+  for (const std::string& name : names) {
+    if (idx < len && buffer_len > 0) {
+      std::memcpy(out_strs[idx], name.c_str(), std::min(name.size() + 1, buffer_len));
+      out_strs[idx][buffer_len - 1] = '\0';
+    }
+    *out_buffer_len = std::max(name.size() + 1, *out_buffer_len);
+    ++idx;
+  }
+  *out_len = idx;
+}
+
+int LGBM_DatasetSetFeatureNames(DatasetHandle handle, const char** feature_names, int num_feature_names) {
+  API_BEGIN();
+  if (!handle || !feature_names) Log::Fatal("LGBM_DatasetSetFeatureNames: NULL argument");
+  std::vector<std::string> names;
+  for (int i = 0; i < num_feature_names; ++i) names.emplace_back(feature_names[i]);
+  reinterpret_cast<Dataset*>(handle)->set_feature_names(names);
+  API_END();
+}
+
+int LGBM_DatasetGetFeatureNames(DatasetHandle handle, const int len, int* num_feature_names, const size_t buffer_len,
+                                size_t* out_buffer_len, char** feature_names) {
+  API_BEGIN();
+  CopyNames(reinterpret_cast<Dataset*>(handle)->feature_names(), len, num_feature_names, buffer_len, out_buffer_len, feature_names);
+  API_END();
+}
+
+int LGBM_DatasetGetField(DatasetHandle handle, const char* field_name, int* out_len, const void** out_ptr, int* out_type) {
+  API_BEGIN();
+  if (!handle || !field_name || !out_len || !out_ptr || !out_type) Log::Fatal("LGBM_DatasetGetField: NULL argument");
+  const Metadata& md = reinterpret_cast<Dataset*>(handle)->metadata();
+  const std::string k(field_name);
+  // Dataset::GetFloatField / GetDoubleField / GetIntField (src/io/dataset.cpp:880-930); "group" returns the boundaries
+  if (k == "label" || k == "target") { *out_ptr = md.label.data(); *out_len = static_cast<int>(md.label.size()); *out_type = C_API_DTYPE_FLOAT32; }
+  else if (k == "weight" || k == "weights") { *out_ptr = md.weights.data(); *out_len = static_cast<int>(md.weights.size()); *out_type = C_API_DTYPE_FLOAT32; }
+  else if (k == "init_score") { *out_ptr = md.init_score.data(); *out_len = static_cast<int>(md.init_score.size()); *out_type = C_API_DTYPE_FLOAT64; }
+  else if (k == "query" || k == "group") { *out_ptr = md.query_boundaries.data(); *out_len = static_cast<int>(md.query_boundaries.size()); *out_type = C_API_DTYPE_INT32; }
+  else Log::Fatal("Field not found");
+  if (*out_len == 0) *out_ptr = nullptr;
+  API_END();
+}
+
+int LGBM_DatasetUpdateParamChecking(const char* old_parameters, const char* new_parameters) {
+  API_BEGIN();
+  // Dataset-construction parameters cannot change once the Dataset exists (src/c_api.cpp:1441-1451 ->
+  // Config::... "Cannot change X after constructed Dataset handle")
+  Config a, b;
+  auto ma = Config::Str2Map(old_parameters);
+  a.Set(ma);
+  auto mb = ma;
+  for (auto& kv : Config::Str2Map(new_parameters)) mb[kv.first] = kv.second;
+  b.Set(mb);
+  if (a.max_bin != b.max_bin) Log::Fatal("Cannot change max_bin after constructed Dataset handle.");
+  if (a.bin_construct_sample_cnt != b.bin_construct_sample_cnt) Log::Fatal("Cannot change bin_construct_sample_cnt after constructed Dataset handle.");
+  if (a.min_data_in_bin != b.min_data_in_bin) Log::Fatal("Cannot change min_data_in_bin after constructed Dataset handle.");
+  if (a.use_missing != b.use_missing) Log::Fatal("Cannot change use_missing after constructed Dataset handle.");
+  if (a.zero_as_missing != b.zero_as_missing) Log::Fatal("Cannot change zero_as_missing after constructed Dataset handle.");
+  if (a.enable_bundle != b.enable_bundle) Log::Fatal("Cannot change enable_bundle after constructed Dataset handle.");
+  if (a.feature_pre_filter != b.feature_pre_filter) Log::Fatal("Cannot change feature_pre_filter after constructed Dataset handle.");
+  if (a.feature_pre_filter && a.min_data_in_leaf < b.min_data_in_leaf)
+    Log::Fatal("Reducing `min_data_in_leaf` with `feature_pre_filter=true` may cause unexpected behaviour for features that were pre-filtered by the larger `min_data_in_leaf`.");
+  API_END();
+}
+
+int LGBM_BoosterLoadModelFromString(const char* model_str, int* out_num_iterations, BoosterHandle* out) {
+  API_BEGIN();
+  if (!model_str || !out_num_iterations || !out) Log::Fatal("LGBM_BoosterLoadModelFromString: NULL argument");
+  std::unique_ptr<Booster> b(new Booster());
+  b->loaded.reset(ParseModel(model_str));
+  *out_num_iterations = static_cast<int>(b->loaded->trees.size());
+  *out = b.release();
+  API_END();
+}
+
+int LGBM_BoosterCreateFromModelfile(const char* filename, int* out_num_iterations, BoosterHandle* out) {
+  API_BEGIN();
+  if (!filename || !out_num_iterations || !out) Log::Fatal("LGBM_BoosterCreateFromModelfile: NULL argument");
+  std::ifstream f(filename, std::ios::binary);
+  if (!f) Log::Fatal("Model file %s is not available for reads", filename);
+  std::stringstream ss;
+  ss << f.rdbuf();
+  std::unique_ptr<Booster> b(new Booster());
+  b->loaded.reset(ParseModel(ss.str()));
+  *out_num_iterations = static_cast<int>(b->loaded->trees.size());
+  *out = b.release();
+  API_END();
+}
+
+int LGBM_BoosterResetParameter(BoosterHandle handle, const char* parameters) {
+  API_BEGIN();
+  Booster* b = reinterpret_cast<Booster*>(handle);
+  GBDT* g = Trainer(handle);
+  std::lock_guard<std::mutex> lock(b->mu);
+  auto merged = g->config().raw;
+  for (auto& kv : Config::Str2Map(parameters)) merged[kv.first] = kv.second;
+  Config c;
+  c.Set(merged);
+  if (!Net().active || Net().num_machines <= 1) c.tree_learner = "serial";
+  g->ResetParameter(c);
+  API_END();
+}
+
+int LGBM_BoosterRollbackOneIter(BoosterHandle handle) {
+  API_BEGIN();
+  Booster* b = reinterpret_cast<Booster*>(handle);
+  GBDT* g = Trainer(handle);
+  std::lock_guard<std::mutex> lock(b->mu);
+  g->RollbackOneIter();
+  API_END();
+}
+
+int LGBM_BoosterGetNumFeature(BoosterHandle handle, int* out_len) {
+  API_BEGIN();
+  Booster* b = reinterpret_cast<Booster*>(handle);
+  *out_len = b->loaded ? b->loaded->max_feature_idx + 1 : b->gbdt->train_data()->num_total_features();
+  API_END();
+}
+
+int LGBM_BoosterGetFeatureNames(BoosterHandle handle, const int len, int* out_len, const size_t buffer_len,
+                                size_t* out_buffer_len, char** out_strs) {
+  API_BEGIN();
+  Booster* b = reinterpret_cast<Booster*>(handle);
+  CopyNames(b->loaded ? b->loaded->feature_names : b->gbdt->train_data()->feature_names(), len, out_len, buffer_len,
+            out_buffer_len, out_strs);
+  API_END();
+}
+
+int LGBM_BoosterFeatureImportance(BoosterHandle handle, int num_iteration, int importance_type, double* out_results) {
+  API_BEGIN();
+  if (importance_type != 0 && importance_type != 1) Log::Fatal("Unknown importance type: only support split=0 and gain=1");
+  Booster* b = reinterpret_cast<Booster*>(handle);
+  std::vector<double> imp;
+  if (b->loaded) {
+    imp.assign(b->loaded->max_feature_idx + 1, 0.0);
+    int n = static_cast<int>(b->loaded->trees.size());
+    if (num_iteration > 0) n = std::min(n, num_iteration);
+    for (int m = 0; m < n; ++m) {
+      const Tree& t = *b->loaded->trees[m];
+      for (int i = 0; i < t.num_leaves() - 1; ++i)
+        if (t.split_gain()[i] > 0) imp[t.split_feature()[i]] += importance_type == 0 ? 1.0 : t.split_gain()[i];
+    }
+  } else {
+    imp = b->gbdt->FeatureImportance(num_iteration, importance_type);
+  }
+  for (size_t i = 0; i < imp.size(); ++i) out_results[i] = imp[i];
+  API_END();
+}
+
+int LGBM_BoosterCalcNumPredict(BoosterHandle handle, int num_row, int predict_type, int start_iteration, int num_iteration,
+                               int64_t* out_len) {
+  API_BEGIN();
+  (void)handle; (void)start_iteration; (void)num_iteration;
+  if (predict_type != C_API_PREDICT_NORMAL && predict_type != C_API_PREDICT_RAW_SCORE)
+    Log::Fatal("predict_type %d is outside this library's path (normal, raw score)", predict_type);
+  *out_len = num_row;   // one class, one value per row
+  API_END();
+}
+
+// The reference's socket / MPI linkers are not part of this library: inside one NVLink box the ranks meet over NCCL.
+int LGBM_NetworkInit(const char* machines, int local_listen_port, int listen_time_out, int num_machines) {
+  API_BEGIN();
+  (void)machines; (void)local_listen_port; (void)listen_time_out;
+  if (num_machines > 1)
+    Log::Fatal("LGBM_NetworkInit (TCP machine list) is not available in this library: data-parallel training runs over "
+               "NCCL -- rank 0 calls LGBM_NetworkGetNCCLUniqueId, every rank LGBM_NetworkInitNCCL(id, rank, num_machines)");
+  API_END();
+}
+
+int LGBM_NetworkInitWithFunctions(int num_machines, int rank, void* reduce_scatter_ext_fun, void* allgather_ext_fun) {
+  API_BEGIN();
+  (void)rank; (void)reduce_scatter_ext_fun; (void)allgather_ext_fun;
+  if (num_machines > 1)
+    Log::Fatal("LGBM_NetworkInitWithFunctions (external collectives on host buffers) is not available in this library: "
+               "the histograms never leave the GPUs; use LGBM_NetworkInitNCCL");
   API_END();
 }
 

@@ -28,8 +28,19 @@ enum MissingType { kMissingNone = 0, kMissingZero = 1, kMissingNaN = 2 };
 
 struct Log {
   static int& level() { static thread_local int lvl = 1; return lvl; }  // verbosity
+  typedef void (*Callback)(const char*);
+  static Callback& callback() { static thread_local Callback cb = nullptr; return cb; }  // LGBM_RegisterLogCallback (log.h:77-80)
   static void write(int lvl, const char* tag, const char* fmt, va_list ap) {
     if (lvl > level()) return;
+    if (callback() != nullptr) {   // the reference hands the pieces of a line to the callback (log.h:134-150)
+      char buf[1024];
+      std::snprintf(buf, sizeof(buf), "[LightGBM-B200] [%s] ", tag);
+      callback()(buf);
+      std::vsnprintf(buf, sizeof(buf), fmt, ap);
+      callback()(buf);
+      callback()("\n");
+      return;
+    }
     std::fprintf(stdout, "[LightGBM-B200] [%s] ", tag);
     std::vfprintf(stdout, fmt, ap);
     std::fprintf(stdout, "\n");

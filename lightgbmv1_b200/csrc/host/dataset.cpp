@@ -3,6 +3,8 @@
 #include <omp.h>
 
 #include <algorithm>
+#include <chrono>
+#include <cstdio>
 #include <cstdlib>
 #include <cstring>
 
@@ -11,6 +13,18 @@
 
 namespace lgb {
 namespace {
+
+// LGBM_B200_TIMING=1: wall-clock of the dataset-construction stages on stderr
+struct DsTimer {
+  bool on; std::chrono::steady_clock::time_point t;
+  DsTimer() : on(std::getenv("LGBM_B200_TIMING") != nullptr), t(std::chrono::steady_clock::now()) {}
+  void tick(const char* what) {
+    if (!on) return;
+    const auto n = std::chrono::steady_clock::now();
+    std::fprintf(stderr, "[b200 timing] dataset: %-22s %8.2f ms\n", what, std::chrono::duration<double, std::milli>(n - t).count());
+    t = n;
+  }
+};
 
 // RowFunctionFromDenseMatric (src/c_api.cpp:2296-2341): element accessor for f32/f64 x row/col-major
 struct MatView {
@@ -168,6 +182,7 @@ Dataset* Dataset::FromDenseMatrix(const void* data, int data_type, int32_t nrow,
   const MatView M{data, data_type, nrow, ncol, row_major};
   std::unique_ptr<Dataset> ds(new Dataset(nrow));
   ds->num_total_features_ = ncol;
+  DsTimer st;
   // sample rows (src/c_api.cpp:1045-1070)
   Random rand(config.data_random_seed);
   const int want = nrow < config.bin_construct_sample_cnt ? nrow : config.bin_construct_sample_cnt;
@@ -175,8 +190,12 @@ Dataset* Dataset::FromDenseMatrix(const void* data, int data_type, int32_t nrow,
   const int sample_cnt = static_cast<int>(sample.size());
   std::vector<std::vector<double>> sample_vals(ncol);
   std::vector<std::vector<int>> sample_idx(ncol);
-  for (int i = 0; i < sample_cnt; ++i) {
-    for (int c = 0; c < ncol; ++c) {
+  // (column by column on the host threads: every column's lists come out in sample order, as in the reference's
+  // row-by-row loop)
+#pragma omp parallel for schedule(dynamic)
+  for (int c = 0; c < ncol; ++c) {
+    sample_vals[c].reserve(sample_cnt); sample_idx[c].reserve(sample_cnt);
+    for (int i = 0; i < sample_cnt; ++i) {
       const double v = M.at(sample[i], c);
       if (std::fabs(v) > kZeroThreshold || std::isnan(v)) {
         sample_vals[c].push_back(v);
@@ -184,6 +203,7 @@ Dataset* Dataset::FromDenseMatrix(const void* data, int data_type, int32_t nrow,
       }
     }
   }
+  st.tick("sample rows");
   // bin mappers (DatasetLoader::ConstructFromSampleData, src/io/dataset_loader.cpp:527-585)
   const data_size_t filter_cnt = static_cast<data_size_t>(static_cast<double>(config.min_data_in_leaf * static_cast<size_t>(sample_cnt)) / nrow);
   std::vector<std::shared_ptr<BinMapper>> all(ncol);
@@ -193,6 +213,7 @@ Dataset* Dataset::FromDenseMatrix(const void* data, int data_type, int32_t nrow,
     all[c]->FindBin(sample_vals[c], static_cast<size_t>(sample_cnt), config.max_bin, config.min_data_in_bin, filter_cnt,
                     config.feature_pre_filter, config.use_missing, config.zero_as_missing);
   }
+  st.tick("FindBin");
   std::vector<int> used;
   for (int c = 0; c < ncol; ++c) if (!all[c]->is_trivial()) used.push_back(c);
   if (used.empty()) Log::Warning("There are no meaningful features, as all feature values are constant.");
@@ -210,7 +231,9 @@ Dataset* Dataset::FromDenseMatrix(const void* data, int data_type, int32_t nrow,
     ds->mappers_.push_back(all[f]);
   }
   for (int c = 0; c < ncol; ++c) ds->feature_names_.push_back("Column_" + std::to_string(c));
+  st.tick("feature order");
   ds->BinAllRows(data, data_type, nrow, ncol, row_major, config.gpu_device_id);
+  st.tick("bin all rows");
   return ds.release();
 }
 
@@ -287,6 +310,14 @@ Dataset::~Dataset() {
   if (label_pinned_) lgbcu_unpin_host_buffer(meta_.label.data());
   if (bins_pinned_) lgbcu_unpin_host_buffer(bins_.data());
   if (dev_bins_) lgbcu_binned_free(dev_bins_);
+}
+
+void Dataset::set_feature_names(const std::vector<std::string>& names) {
+  if (static_cast<int>(names.size()) != num_total_features_) Log::Fatal("Size of feature_names error, should equal with total number of features");
+  feature_names_ = names;
+  for (std::string& n : feature_names_) {   // spaces would break the model text (the reference replaces them and warns)
+    for (char& ch : n) if (ch == ' ') ch = '_';
+  }
 }
 
 uint64_t Dataset::num_total_bin() const {

@@ -48,6 +48,7 @@ class Dataset {
   Metadata& metadata() { return meta_; }
   const Metadata& metadata() const { return meta_; }
   const std::vector<std::string>& feature_names() const { return feature_names_; }
+  void set_feature_names(const std::vector<std::string>& names);  // Dataset::set_feature_names (dataset.h:621-652)
   std::vector<std::string> feature_infos() const;
   // value of feature `real` in bin space for one raw value (used by prediction on binned data)
   uint32_t stored_value(int inner, double v) const;

@@ -411,6 +411,46 @@ void GBDT::PredictMat(const void* data, int data_type, int32_t nrow, int32_t nco
   }
 }
 
+void GBDT::RollbackOneIter() {
+  if (models_.empty()) return;
+  Tree& t = *models_.back();
+  t.ScaleLeafValues(-1.0);   // Tree::Shrinkage(-1): subtracting the tree = adding its negative
+  std::vector<int> thr(t.threshold_in_bin().begin(), t.threshold_in_bin().end());
+  Check(lgbcu_add_score_by_tree(ctx_, t.num_leaves(), t.split_feature_inner().data(), thr.data(), t.decision_type().data(),
+                                t.left_child().data(), t.right_child().data(), t.leaf_values().data(), nullptr, 0, 0));
+  AddTreeToValid(t);
+  models_.pop_back();
+  --iter_;
+}
+
+void GBDT::ResetParameter(const Config& merged) {
+  if (merged.objective != config_.objective || merged.boosting != config_.boosting || merged.tree_learner != config_.tree_learner ||
+      merged.max_bin != config_.max_bin || merged.num_leaves > config_.num_leaves)
+    Log::Fatal("LGBM_BoosterResetParameter: only the learning rate and the tree-growing parameters (num_leaves not above the "
+               "value the booster was created with) can be reset on this booster");
+  config_ = merged;
+  shrinkage_rate_ = config_.learning_rate;
+  LgbCuTreeParams tp;
+  tp.num_leaves = config_.num_leaves; tp.max_depth = config_.max_depth; tp.min_data_in_leaf = config_.min_data_in_leaf;
+  tp.reserved = 0; tp.min_sum_hessian_in_leaf = config_.min_sum_hessian_in_leaf; tp.lambda_l1 = config_.lambda_l1;
+  tp.lambda_l2 = config_.lambda_l2; tp.min_gain_to_split = config_.min_gain_to_split;
+  tp.max_delta_step = config_.max_delta_step; tp.path_smooth = config_.path_smooth;
+  Check(lgbcu_set_tree_params(ctx_, &tp));
+}
+
+std::vector<double> GBDT::FeatureImportance(int num_iteration, int importance_type) const {
+  std::vector<double> imp(train_->num_total_features(), 0.0);
+  int n_models = static_cast<int>(models_.size());
+  if (num_iteration > 0) n_models = std::min(n_models, num_iteration);
+  for (int m = 0; m < n_models; ++m) {
+    const Tree& t = *models_[m];
+    for (int i = 0; i < t.num_leaves() - 1; ++i) {
+      if (t.split_gain()[i] > 0) imp[t.split_feature()[i]] += importance_type == 0 ? 1.0 : t.split_gain()[i];
+    }
+  }
+  return imp;
+}
+
 std::vector<double> GBDT::FeatureImportanceSplit(int num_iteration) const {
   std::vector<double> imp(train_->num_total_features(), 0.0);
   int n_models = static_cast<int>(models_.size());

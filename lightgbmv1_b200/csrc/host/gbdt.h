@@ -43,6 +43,14 @@ class GBDT {
   void PredictMat(const void* data, int data_type, int32_t nrow, int32_t ncol, bool row_major, bool raw_score,
                   int num_iteration, double* out) const;
   std::string SaveModelToString(int start_iteration, int num_iteration) const;
+  // GBDT::RollbackOneIter (src/boosting/gbdt.cpp:421-444): the last tree leaves the scores and the model
+  void RollbackOneIter();
+  // Booster::ResetConfig (src/c_api.cpp:232-283) for the parameters that can change while training: learning rate
+  // and the tree-growing parameters; anything that would change the data or the objective is refused
+  void ResetParameter(const Config& merged);
+  // GBDT::FeatureImportance (src/boosting/gbdt_model_text.cpp:576-620): 0 = split counts, 1 = total gains
+  std::vector<double> FeatureImportance(int num_iteration, int importance_type) const;
+  const Dataset* train_data() const { return train_; }
   const Config& config() const { return config_; }
   LgbCuContext* device() const { return ctx_; }
   int64_t total_device_launches() const;

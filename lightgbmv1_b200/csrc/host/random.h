@@ -27,12 +27,28 @@ class Random {
         if (NextFloat() < prob) ret.push_back(i);
       }
     } else {
-      std::set<int> picked;
+      // Floyd's sampling as in random.h:85-95; the reference keeps the picks in a std::set and returns them in
+      // ascending order -- a bitmap over 0..N-1 gives the same set and the same order without the tree
+      std::vector<unsigned long long> picked((static_cast<size_t>(N) + 63) / 64, 0ull);
+      auto test_and_set = [&](int v) {
+        unsigned long long& w = picked[static_cast<size_t>(v) >> 6];
+        const unsigned long long bit = 1ull << (v & 63);
+        const bool was = (w & bit) != 0;
+        w |= bit;
+        return was;
+      };
       for (int r = N - K; r < N; ++r) {
         const int v = NextInt(0, r);
-        if (!picked.insert(v).second) picked.insert(r);
+        if (test_and_set(v)) test_and_set(r);
       }
-      ret.assign(picked.begin(), picked.end());
+      for (size_t w = 0; w < picked.size(); ++w) {
+        unsigned long long bits = picked[w];
+        while (bits) {
+          const int b = __builtin_ctzll(bits);
+          ret.push_back(static_cast<int>(w * 64 + b));
+          bits &= bits - 1;
+        }
+      }
     }
     return ret;
   }

@@ -1,5 +1,9 @@
 #include "tree.h"
 
+#include <cstdlib>
+#include <memory>
+#include <unordered_map>
+
 namespace lgb {
 
 static inline double MaybeRoundToZero(double v) { return (v >= -kZeroThreshold && v <= kZeroThreshold) ? 0 : v; }
@@ -93,6 +97,56 @@ std::string Tree::ToString() const {
   o << "shrinkage=" << shrinkage_ << '\n';
   o << '\n';
   return o.str();
+}
+
+Tree* Tree::FromString(const std::string& text) {
+  std::unordered_map<std::string, std::string> kv;
+  size_t pos = 0;
+  while (pos < text.size()) {
+    size_t e = text.find('\n', pos);
+    if (e == std::string::npos) e = text.size();
+    const std::string line = text.substr(pos, e - pos);
+    pos = e + 1;
+    const size_t eq = line.find('=');
+    if (eq != std::string::npos) kv[line.substr(0, eq)] = line.substr(eq + 1);
+  }
+  auto need = [&](const char* k) -> const std::string& {
+    auto it = kv.find(k);
+    if (it == kv.end()) Log::Fatal("Tree model string format error, should contain %s field", k);
+    return it->second;
+  };
+  const int nl = std::atoi(need("num_leaves").c_str());
+  if (kv.count("num_cat") && std::atoi(kv["num_cat"].c_str()) > 0) Log::Fatal("categorical splits are outside this library's path");
+  std::unique_ptr<Tree> t(new Tree(std::max(nl, 2)));
+  t->num_leaves_ = nl;
+  auto doubles = [](const std::string& s, size_t n, std::vector<double>* out) {
+    const char* p = s.c_str(); char* end = nullptr;
+    for (size_t i = 0; i < n; ++i) { (*out)[i] = std::strtod(p, &end); p = end; }
+  };
+  auto ints = [](const std::string& s, size_t n, std::vector<int>* out) {
+    const char* p = s.c_str(); char* end = nullptr;
+    for (size_t i = 0; i < n; ++i) { (*out)[i] = static_cast<int>(std::strtol(p, &end, 10)); p = end; }
+  };
+  const size_t ni = static_cast<size_t>(std::max(nl - 1, 0)), nlz = static_cast<size_t>(nl);
+  doubles(need("leaf_value"), nlz, &t->leaf_value_);
+  if (nl > 1) {
+    ints(need("split_feature"), ni, &t->split_feature_);
+    t->split_feature_inner_ = t->split_feature_;
+    doubles(need("threshold"), ni, &t->threshold_);
+    std::vector<int> dt(ni); ints(need("decision_type"), ni, &dt);
+    for (size_t i = 0; i < ni; ++i) t->decision_type_[i] = static_cast<int8_t>(dt[i]);
+    ints(need("left_child"), ni, &t->left_child_);
+    ints(need("right_child"), ni, &t->right_child_);
+    std::vector<double> tmp(ni);
+    if (kv.count("split_gain")) { doubles(kv["split_gain"], ni, &tmp); for (size_t i = 0; i < ni; ++i) t->split_gain_[i] = static_cast<float>(tmp[i]); }
+    if (kv.count("leaf_weight")) doubles(kv["leaf_weight"], nlz, &t->leaf_weight_);
+    if (kv.count("leaf_count")) ints(kv["leaf_count"], nlz, &t->leaf_count_);
+    if (kv.count("internal_value")) doubles(kv["internal_value"], ni, &t->internal_value_);
+    if (kv.count("internal_weight")) doubles(kv["internal_weight"], ni, &t->internal_weight_);
+    if (kv.count("internal_count")) ints(kv["internal_count"], ni, &t->internal_count_);
+  }
+  if (kv.count("shrinkage")) t->shrinkage_ = std::strtod(kv["shrinkage"].c_str(), nullptr);
+  return t.release();
 }
 
 // Tree::Predict -> GetLeaf -> NumericalDecision (include/LightGBM/tree.h:250-283)

@@ -20,6 +20,9 @@ class Tree {
   void AddBias(double val);
   void AsConstantTree(double val) { num_leaves_ = 1; shrinkage_ = 1.0f; leaf_value_[0] = val; }
   std::string ToString() const;
+  // the inverse of ToString (Tree::Tree(const char* str, size_t*), src/io/tree.cpp:580-700): a tree of a saved model,
+  // good for Predict / ToString (bin-space thresholds are not part of the text)
+  static Tree* FromString(const std::string& text);
   double Predict(const double* features) const;  // raw feature values (Tree::Predict / NumericalDecision)
 
   int num_leaves() const { return num_leaves_; }
@@ -32,6 +35,7 @@ class Tree {
   const std::vector<int>& left_child() const { return left_child_; }
   const std::vector<int>& right_child() const { return right_child_; }
   const std::vector<float>& split_gain() const { return split_gain_; }
+  void ScaleLeafValues(double rate) { Shrinkage(rate); }
 
   static const int8_t kDefaultLeftMask = 2;  // include/LightGBM/tree.h: kCategoricalMask = 1, kDefaultLeftMask = 2
 

@@ -1,0 +1,114 @@
+"""Boundary proof: the reference's OWN python package (python-package/lightgbm, unmodified, read
+from /root/reference -- absent on the GPU box, where this test is skipped) bound to lib_lightgbm_b200.so instead of
+lib_lightgbm.so.  lgb.train on a numpy matrix must run through every LGBM_* call basic.py / engine.py make and give the
+model the reference library gives.  The CPU half checks that every symbol that path touches is exported."""
+import ctypes as C
+import importlib
+import os
+import re
+import sys
+
+import numpy as np
+import pytest
+
+import capi
+import helpers as H
+
+PKG = os.environ.get("LGBM_REF_PYTHON_PACKAGE", "/root/reference/python-package")   # (absent on the GPU box)
+
+
+def _train_path_symbols():
+    """LGBM_* names used by the functions lgb.train(params, lgb.Dataset(X, y)) executes (found by tracing the package
+    on the reference library once; kept as a list so that the check needs no reference tree)."""
+    return ["LGBM_GetLastError", "LGBM_RegisterLogCallback", "LGBM_DatasetCreateFromMat", "LGBM_DatasetSetField", "LGBM_DatasetGetField",
+            "LGBM_DatasetSetFeatureNames", "LGBM_DatasetGetFeatureNames", "LGBM_DatasetUpdateParamChecking",
+            "LGBM_DatasetGetNumData", "LGBM_DatasetGetNumFeature", "LGBM_DatasetFree", "LGBM_BoosterCreate",
+            "LGBM_BoosterFree", "LGBM_BoosterAddValidData", "LGBM_BoosterGetNumClasses", "LGBM_BoosterGetEvalCounts",
+            "LGBM_BoosterGetEvalNames", "LGBM_BoosterGetEval", "LGBM_BoosterUpdateOneIter", "LGBM_BoosterUpdateOneIterCustom",
+            "LGBM_BoosterRollbackOneIter", "LGBM_BoosterGetCurrentIteration", "LGBM_BoosterNumModelPerIteration",
+            "LGBM_BoosterNumberOfTotalModel", "LGBM_BoosterResetParameter", "LGBM_BoosterSaveModelToString",
+            "LGBM_BoosterLoadModelFromString", "LGBM_BoosterGetNumFeature", "LGBM_BoosterGetFeatureNames",
+            "LGBM_BoosterFeatureImportance", "LGBM_BoosterPredictForMat", "LGBM_BoosterCalcNumPredict",
+            "LGBM_BoosterGetPredict", "LGBM_BoosterGetNumPredict", "LGBM_BoosterSaveModel", "LGBM_NetworkInit", "LGBM_NetworkFree"]
+
+
+def test_every_symbol_of_the_python_train_path_is_exported():
+    lib = C.CDLL(capi.OURS_SO)
+    missing = [n for n in _train_path_symbols() if not hasattr(lib, n)]
+    assert not missing, missing
+
+
+def test_loaded_model_round_trip_and_prediction_cpu():
+    """LGBM_BoosterLoadModelFromString on a model the REFERENCE trained: same predictions as the reference, same text back"""
+    if not H.have_ref():
+        pytest.skip("oracle/_ref not built")
+    rng = np.random.default_rng(3)
+    X = rng.standard_normal((4000, 8)); X[::9, 2] = np.nan
+    y = (np.nan_to_num(X[:, 0]) + X[:, 1] ** 2 > 1).astype(np.float32)
+    ref, ours = capi.reference(), capi.ours()
+    _, br, _ = capi.train(ref, X, y, "objective=binary num_leaves=15 verbosity=-1 num_threads=2", 6)
+    text = ref.model_string(br)
+    bo = ours.load_model_from_string(text)
+    for raw in (True, False):
+        np.testing.assert_allclose(ours.predict_mat(bo, X, raw=raw), ref.predict_mat(br, X, raw=raw), rtol=0, atol=1e-15)
+    assert ours.model_string(bo) == text
+    n = C.c_int()
+    ours.check(ours.lib.LGBM_BoosterGetNumFeature(bo, C.byref(n))); assert n.value == 8
+    imp_o = np.zeros(8); imp_r = np.zeros(8)
+    ours.check(ours.lib.LGBM_BoosterFeatureImportance(bo, C.c_int(-1), C.c_int(1), imp_o.ctypes.data_as(C.POINTER(C.c_double))))
+    ref.check(ref.lib.LGBM_BoosterFeatureImportance(br, C.c_int(-1), C.c_int(1), imp_r.ctypes.data_as(C.POINTER(C.c_double))))
+    np.testing.assert_allclose(imp_o, imp_r, rtol=1e-6)   # the text keeps the gains with 6 significant digits
+    with pytest.raises(capi.LGBMError, match="loaded from a model string"):
+        ours.update(bo)
+    with pytest.raises(capi.LGBMError, match="LGBM_NetworkInitNCCL"):
+        ours.check(ours.lib.LGBM_NetworkInit(C.c_char_p(b"127.0.0.1:1,127.0.0.1:2"), C.c_int(1), C.c_int(1), C.c_int(2)))
+
+
+def _package_bound_to(so_path, name):
+    """import the reference's python package (its files, unmodified) with its library lookup pointed at `so_path`:
+    lightgbm/libpath.py is loaded first and its find_lib_path replaced, then the package's own __init__ runs"""
+    import importlib.util
+    pkg_dir = os.path.join(PKG, "lightgbm")
+    if not os.path.isdir(pkg_dir):
+        pytest.skip("reference python package not present")
+    for k in [k for k in sys.modules if k == "lightgbm" or k.startswith("lightgbm.")]:
+        del sys.modules[k]
+    spec = importlib.util.spec_from_file_location("lightgbm", os.path.join(pkg_dir, "__init__.py"),
+                                                  submodule_search_locations=[pkg_dir])
+    pkg = importlib.util.module_from_spec(spec)
+    sys.modules["lightgbm"] = pkg
+    lspec = importlib.util.spec_from_file_location("lightgbm.libpath", os.path.join(pkg_dir, "libpath.py"))
+    libpath = importlib.util.module_from_spec(lspec)
+    lspec.loader.exec_module(libpath)
+    libpath.find_lib_path = lambda: [so_path]
+    sys.modules["lightgbm.libpath"] = libpath
+    spec.loader.exec_module(pkg)
+    return pkg
+
+
+@pytest.mark.gpu
+def test_lgb_train_through_the_reference_python_package():
+    if not H.have_ref():
+        pytest.skip("oracle/_ref not built")
+    rng = np.random.default_rng(5)
+    X = rng.standard_normal((30_000, 10)).astype(np.float32)
+    y = (X[:, 0] * X[:, 1] + X[:, 2] > 0).astype(np.float32)
+    Xv, yv = X[:5000], y[:5000]
+    params = {"objective": "binary", "num_leaves": 31, "learning_rate": 0.1, "metric": ["binary_logloss", "auc"], "verbosity": -1}
+    out = []
+    for so, extra in ((capi.REF_SO, {"force_col_wise": True, "num_threads": 4}), (capi.OURS_SO, {})):
+        lgb = _package_bound_to(so, so)
+        dtrain = lgb.Dataset(X, label=y, feature_name=[f"f{i}" for i in range(10)])
+        dvalid = lgb.Dataset(Xv, label=yv, reference=dtrain)
+        evals = {}
+        bst = lgb.train({**params, **extra}, dtrain, num_boost_round=12, valid_sets=[dvalid], valid_names=["v"],
+                        evals_result=evals, verbose_eval=False)
+        out.append((bst.model_to_string(), bst.predict(Xv), evals, bst.feature_importance("gain"), bst.feature_name()))
+    (mr, pr, er, ir, nr), (mo, po, eo, io_, no) = out
+    same, n, first = capi.compare_models(mr, mo, rtol_value=H.VALUE_RTOL)
+    assert n == 12 and same == n, first
+    np.testing.assert_allclose(po, pr, rtol=0, atol=1e-9)
+    assert nr == no
+    np.testing.assert_allclose(io_, ir, rtol=1e-6)
+    for k in ("binary_logloss", "auc"):
+        np.testing.assert_allclose(eo["v"][k], er["v"][k], rtol=1e-9)
