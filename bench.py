@@ -172,6 +172,80 @@ def run_reference(args):
     return 0
 
 
+CONFIG5_ROWS = 100_000_000
+
+
+def gen_rows_threaded(n, seed, threads):
+    """config #2's generator, 1M-row chunks drawn by a few python threads (numpy releases the GIL)"""
+    from concurrent.futures import ThreadPoolExecutor
+    X = np.empty((n, N_FEAT), dtype=np.float32)
+    y = np.empty(n, dtype=np.float32)
+    w = np.random.default_rng(1).standard_normal(N_FEAT).astype(np.float32)
+    levels = np.array([0.0, 1.087, 2.173], dtype=np.float32)
+    chunk = 1 << 20
+    starts = list(range(0, n, chunk))
+
+    def fill(i):
+        s_, e_ = starts[i], min(n, starts[i] + chunk)
+        rng = np.random.default_rng([seed, i])
+        b = rng.standard_normal((e_ - s_, N_FEAT), dtype=np.float32)
+        b[:, 21:25] = np.maximum(0, b[:, 21:25])
+        b[:, 25:28] = levels[rng.integers(0, 3, size=(e_ - s_, 3))]
+        X[s_:e_] = b
+        y[s_:e_] = ((b @ w + 0.5 * b[:, 0] * b[:, 1] + rng.standard_normal(e_ - s_, dtype=np.float32)) > 0)
+
+    with ThreadPoolExecutor(max_workers=max(1, threads)) as ex:
+        list(ex.map(fill, range(len(starts))))
+    return X, y
+
+
+def run_config5(ours, lib, rank, world, local, host_threads, total_rows, barrier, allmax):
+    """BASELINE.json configs[4]: Higgs-shaped 100M x 28 rows sharded over the ranks (each rank generates only its
+    shard), tree_learner=data; the common bin mappers come from a 200k-row sample every rank draws identically."""
+    t_all = time.perf_counter()
+    rows = total_rows // world
+    Xr, _ = gen_rows_threaded(200_000, 555, host_threads)
+    dsp = PARAMS + f" num_threads={host_threads} gpu_device_id={local}"
+    ref_ds = ours.dataset_from_mat(Xr, dsp)
+    Xs, ys = gen_rows_threaded(rows, 1000 + rank, host_threads)
+    t_gen = time.perf_counter() - t_all
+    t0 = time.perf_counter()
+    ds = ours.dataset_from_mat(Xs, dsp, reference=ref_ds)
+    ours.set_field(ds, "label", ys)
+    t_ds = time.perf_counter() - t0
+    del Xs
+    params = dsp + (f" tree_learner=data num_machines={world}" if world > 1 else "")
+    b = ours.booster_create(ds, params)
+    for _ in range(2):
+        ours.update(b)
+    barrier()
+    t0 = time.perf_counter()
+    k = 5
+    for _ in range(k):
+        ours.update(b)
+    barrier()
+    dt = allmax(time.perf_counter() - t0)
+    hist_ms, hist_calls, hist_bytes = C.c_double(), C.c_int64(), C.c_double()
+    ours.check(lib.LGBM_B200_BoosterProfile(b, 1, 1, C.byref(hist_ms), C.byref(hist_calls), C.byref(hist_bytes)))
+    ours.update(b)
+    ph = (C.c_double * 8)()
+    ours.check(lib.LGBM_B200_BoosterPhases(b, ph))
+    ours.check(lib.LGBM_B200_BoosterProfile(b, 0, 0, C.byref(hist_ms), C.byref(hist_calls), C.byref(hist_bytes)))
+    ours.booster_free(b); ours.dataset_free(ds); ours.dataset_free(ref_ds)
+    peak = 6650.0
+    try:
+        peak = float(json.load(open(os.path.join(ROOT, "MEASURED_PEAKS.json"))).get("hbm_gbs", peak))
+    except Exception:
+        pass
+    ach = (hist_bytes.value / 1e9) / (hist_ms.value / 1e3) if hist_ms.value > 0 else 0.0
+    return {"workload": f"Higgs-shaped {total_rows}x{N_FEAT}, rows sharded over {world} rank(s), tree_learner=data (configs[4])",
+            "rows_total": rows * world, "rows_per_gpu": rows, "iterations_timed": k, "ms_per_iter": 1e3 * dt / k,
+            "iters_per_s": k / dt, "hist_frac_of_hbm_peak": ach / peak, "hist_kernel_ms_per_iter": ph[1],
+            "hist_plus_allreduce_ms_per_iter": ph[0], "find_split_ms_per_iter": ph[2], "partition_ms_per_iter": ph[4],
+            "rounds_per_tree": ph[7], "generate_s": t_gen, "dataset_create_s": t_ds,
+            "dataset_create_h2d_gb_per_s": rows * N_FEAT * 4 / 1e9 / t_ds if t_ds > 0 else None}
+
+
 def model_hash(text):
     return int(hashlib.sha256(text.split("feature_importances")[0].encode()).hexdigest()[:15], 16)
 
@@ -328,6 +402,20 @@ def run_ours(args):
                              "semantics, same bin mappers, boost_from_average=false)",
                      "trees_compared": ntrees, "trees_identical": same, "first_mismatch": first,
                      "dp_equals_single": bool(same == ntrees and ntrees == DP_CHECK_ITERS), "all_ranks_agree": bool(ranks_agree)}
+        config5 = None
+        if not args.no_config5:
+            ours.dataset_free(ds)
+            if ds_full is not None:
+                ours.dataset_free(ds_full)
+
+            def allmax(v):
+                t5 = torch.tensor([v], dtype=torch.float64, device="cuda")
+                dist.all_reduce(t5, op=dist.ReduceOp.MAX)
+                return float(t5[0])
+            try:
+                config5 = run_config5(ours, lib, rank, world, local, host_threads, args.config5_rows, barrier, allmax)
+            except Exception as ex:  # the headline line must still be printed
+                config5 = {"error": str(ex)[:300]}
         dist.barrier()
         ours.check(lib.LGBM_NetworkFree())
         dist.destroy_process_group()
@@ -365,6 +453,15 @@ def run_ours(args):
                  "trees_compared": ntrees, "trees_identical": same, "first_mismatch": first,
                  "max_abs_score_diff": float(np.max(np.abs(pred_ref - pred_ours))),
                  "logloss_reference": ll(p0), "logloss_ours": ll(p1)}
+    if world == 1:
+        config5 = None
+        if not args.no_config5:
+            ours.dataset_free(ds)
+            X = y = X_e2e = None
+            try:
+                config5 = run_config5(ours, lib, 0, 1, local, host_threads, args.config5_rows, lambda: None, lambda v: v)
+            except Exception as ex:
+                config5 = {"error": str(ex)[:300]}
     line = {
         "metric": "boosting iters/sec", "value": args.steps / dt, "unit": "iters/s", "n_gpus": world,
         "steps": args.steps, "warmup": args.warmup, "ms_per_step": 1e3 * dt / args.steps, "higher_is_better": True,
@@ -392,6 +489,7 @@ def run_ours(args):
                                "rounds": phases[7] / prof_iters},
         "cpu_baseline": cpu,
         "train_check": check,
+        "extra": {"config5": config5},
     }
     emit(line)
     return 0
@@ -405,6 +503,8 @@ def main():
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
     ap.add_argument("--rows", type=int, default=N_ROWS)
     ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--no-config5", action="store_true", help="skip the 100M-row data-parallel workload (extra.config5)")
+    ap.add_argument("--config5-rows", type=int, default=CONFIG5_ROWS)
     args = ap.parse_args()
     if args.warmup < 3:
         args.warmup = 3
