@@ -113,8 +113,8 @@ struct DevView {
   int num_data, num_features, row_stride, total_bin, num_tiles16;
   int data_parallel;         // 1: histograms are all-reduced across ranks, leaf counts are the global estimates
   const uint8_t* bins;
-  const uint8_t* bins_col;   // column-major copy [F][col_stride]: the partition of a large leaf reads one feature of
-  long long col_stride;      // (nearly) consecutive rows -- 32 rows per sector instead of one
+  const uint8_t* bins_col;   // column-major copy [F][col_stride]: the partition reads ONE feature of a leaf's rows -- a
+  long long col_stride;      // sector of this copy holds that feature of 32 neighbouring rows, a sector of `bins` of one
   const DevFeat* feats;
   const int8_t* feat_used;   // ColSampler by-tree mask
   int8_t* splittable;        // [num_leaves slots][num_features]  FeatureHistogram::is_splittable_
