@@ -100,6 +100,15 @@ struct DevCtl {
   long long global_root;  // root rows over all ranks   } adjacent: one 2 x int64 sum all-reduce
   long long global_rows;  // dataset rows over all ranks }
   unsigned long long prof_hist_rows, prof_hist_rows_indexed, prof_hist_calls, prof_hist_ns;
+  // what k_hist builds in the current round, written by k_partition (part_expand): per item the rows of the smaller
+  // child (0 = nothing to build) and the child itself -- one dependent load for k_hist's preamble instead of the
+  // item_leaf -> spec -> child chain
+  int hist_rows[LGB_KMAX];
+  DevLeaf hist_leaf[LGB_KMAX];
+  // what k_partition splits in the current round, written by the control step of k_find_split after its commits:
+  // the items' leaves and the descriptors of their split features (again one dependent load instead of a chain)
+  DevLeaf item_rec[LGB_KMAX];
+  DevFeat item_feat[LGB_KMAX];
 };
 
 struct DevParams {   // LgbCuTreeParams + derived switches
@@ -144,9 +153,11 @@ struct DevView {
 #ifdef LGBCU_STAGE_TIMERS
 __device__ unsigned long long g_stamps[3 * 4096];
 __device__ __forceinline__ void stamp(const DevCtl* c, int k) {
-  if (blockIdx.x == 0 && blockIdx.y == 0 && threadIdx.x == 0 && c->num_splits < 4096) {
+  // indexed by the round of tree growth (the control step of k_find_split has already bumped it when k_partition runs)
+  const int r = c->round - (k == 2 ? 1 : 0);
+  if (blockIdx.x == 0 && blockIdx.y == 0 && threadIdx.x == 0 && r >= 0 && r < 4096 && !c->done) {
     unsigned long long t; asm volatile("mov.u64 %0, %globaltimer;" : "=l"(t));
-    g_stamps[3 * c->num_splits + k] = t;
+    g_stamps[3 * r + k] = t;
   }
 }
 __device__ unsigned long long g_ends[3 * 4096];

@@ -49,6 +49,7 @@
 
 #ifdef LGBCU_STAGE_TIMERS
 __device__ unsigned long long g_hist_cycles[8];
+__device__ long long g_hist_t0;
 #define HSTAGE(i) do { if (blockIdx.x == 0 && threadIdx.x == 0) { long long t_ = clock64(); g_hist_cycles[i] += (unsigned long long)(t_ - ht_); ht_ = t_; } } while (0)
 #else
 #define HSTAGE(i) do {} while (0)
@@ -155,6 +156,7 @@ __device__ void hist_shared_path(const DevView& V, const DevLeaf& L, bool identi
   const double sg = V.ctl->scale_g, sh = V.ctl->scale_h;
 #ifdef LGBCU_STAGE_TIMERS
   long long ht_ = clock64();
+  if (blockIdx.x == 0 && threadIdx.x == 0) g_hist_cycles[5] += (unsigned long long)(ht_ - g_hist_t0);
 #endif
   for (int unit = cluster_id; unit < NG * PG; unit += nclusters) {
     const int group = unit / NG, fg = unit - group * NG, part = group * HIST_CLUSTER + rank;
@@ -284,6 +286,9 @@ __device__ void hist_phase(const DevView& V, const DevLeaf& L, bool is_root, int
 __global__ void __cluster_dims__(HIST_CLUSTER, 1, 1) __launch_bounds__(HIST_THREADS, HIST_BLOCKS_PER_SM) k_hist(DevView V, int leaf_arg, int mode, int min_rows, int small_rows) {
   extern __shared__ __align__(16) unsigned char hist_smem[];
   const DevCtl* c = V.ctl;
+#ifdef LGBCU_STAGE_TIMERS
+  if (blockIdx.x == 0 && threadIdx.x == 0) g_hist_t0 = clock64();
+#endif
   STAMP(V.ctl, 0);
   // which leaf this block works for, and as which block of how many (one call site below: the body is large)
   DevLeaf L; bool is_root = false; int bid = blockIdx.x, nblocks = gridDim.x;
@@ -300,34 +305,32 @@ __global__ void __cluster_dims__(HIST_CLUSTER, 1, 1) __launch_bounds__(HIST_THRE
       const int ni = c->num_items;
       const int nclusters = (int)gridDim.x / HIST_CLUSTER;
       const int my_cluster = (int)blockIdx.x / HIST_CLUSTER, rank = (int)blockIdx.x % HIST_CLUSTER;
-      long long rows[LGB_KMAX];
+      int rows[LGB_KMAX];
       long long total = 0;
       int live = 0;
 #pragma unroll
       for (int e = 0; e < LGB_KMAX; ++e) {
-        rows[e] = 0;
-        if (e < ni) {
-          const DevSpec* S = &V.spec[c->item_leaf[e]];
-          if (!S->skip_find) { rows[e] = S->child[S->smaller].count > 0 ? S->child[S->smaller].count : 1; total += rows[e]; ++live; }
-        }
+        rows[e] = e < ni ? c->hist_rows[e] : 0;
+        total += rows[e]; live += rows[e] != 0;
       }
       if (live == 0) return;
       const int spare = nclusters - live;
-      int off = 0;
-      bool found = false;
+      // floor(rows * spare / total) without a 64-bit division: scaled down a hair so that float rounding can never
+      // hand out more clusters than there are (every block computes the same numbers)
+      const float share = (float)spare / (float)total * 0.99999f;
+      int off = 0, mine = -1;
 #pragma unroll
       for (int e = 0; e < LGB_KMAX; ++e) {
-        if (rows[e] == 0 || found) continue;
-        const int nc = 1 + (int)(rows[e] * spare / total);
-        if (my_cluster >= off && my_cluster < off + nc) {
-          const DevSpec* S = &V.spec[c->item_leaf[e]];
-          L = S->child[S->smaller];
+        if (rows[e] == 0) continue;
+        const int nc = 1 + (int)((float)rows[e] * share);
+        if (mine < 0 && my_cluster >= off && my_cluster < off + nc) {
+          mine = e;
           bid = (my_cluster - off) * HIST_CLUSTER + rank; nblocks = nc * HIST_CLUSTER;
-          found = true;
         }
         off += nc;
       }
-      if (!found) return;
+      if (mine < 0) return;
+      L = c->hist_leaf[mine];
     }
   }
   hist_phase(V, L, is_root, mode, min_rows, small_rows, bid, nblocks, hist_smem);

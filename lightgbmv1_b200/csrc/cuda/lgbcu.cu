@@ -1089,6 +1089,7 @@ extern "C" int lgbcu_debug_stamps(unsigned long long* out, int n) {
   cudaMemcpyFromSymbol(out + n, g_ends, sizeof(unsigned long long) * (size_t)n);
   static unsigned long long z[3 * 4096];
   cudaMemcpyToSymbol(g_ends, z, sizeof(z));
+  cudaMemcpyToSymbol(g_stamps, z, sizeof(z));
   return 0;
 }
 extern "C" int lgbcu_debug_hist_stages(unsigned long long* out8, int reset) {

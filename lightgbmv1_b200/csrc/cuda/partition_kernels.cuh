@@ -101,12 +101,15 @@ __device__ void part_expand(const DevView& V, int e, int leaf, const DevLeaf& L,
   const int fresh = 1 + (c->round - 1) * c->lookahead + e;
   int smaller;
   if (gl < gr) { smaller = 0; A.slot = fresh; B.slot = L.slot; }
-  else { smaller = 1; B.slot = fresh; A.slot = L.slot; }  // the scatter wrote the smaller side's ordered (gq, hq)
+  else { smaller = 1; B.slot = fresh; A.slot = L.slot; }
   int skip = 0;
   if (V.p.max_depth > 0 && A.depth >= V.p.max_depth) skip = 1;
   if (!skip && gr < V.p.min_data_in_leaf * 2 && gl < V.p.min_data_in_leaf * 2) skip = 1;
   S->child[0] = A; S->child[1] = B;
   S->left_count = left_cnt; S->smaller = smaller; S->skip_find = skip;
+  const DevLeaf& Sm = smaller == 0 ? A : B;
+  c->hist_leaf[e] = Sm;
+  c->hist_rows[e] = skip ? 0 : (Sm.count > 0 ? Sm.count : 1);
 }
 
 // ---------------------------------------------------------------------------------------------------------------
@@ -150,19 +153,20 @@ __global__ void __launch_bounds__(PART_THREADS, PART_BLOCKS_PER_SM + 1) k_partit
     }
     // the grid's blocks are dealt to the items in proportion to their 1024-row tiles; one control block per item
     int tiles[LGB_KMAX];
-    long long T = 0;
+    int T = 0;
 #pragma unroll
     for (int i = 0; i < LGB_KMAX; ++i) {
-      tiles[i] = 0;
-      if (i < ni) { tiles[i] = (V.leaves[c->item_leaf[i]].count + PART_TILE - 1) / PART_TILE; T += tiles[i]; }
+      tiles[i] = i < ni ? (c->item_rec[i].count + PART_TILE - 1) / PART_TILE : 0;
+      T += tiles[i];
     }
-    const long long share = (long long)gridDim.x - 2 * ni;
+    // floor(tiles * share / T) in float, scaled down a hair so that rounding never hands out more blocks than there are
+    const float share = T > 0 ? (float)((int)gridDim.x - 2 * ni) / (float)T * 0.99999f : 0.f;
     int off = 0;
     bool found = false;
 #pragma unroll
     for (int i = 0; i < LGB_KMAX; ++i) {
       if (i < ni && !found) {
-        int nb = (int)(T > 0 ? (long long)tiles[i] * share / T : 0);
+        int nb = (int)((float)tiles[i] * share);
         if (nb < 1) nb = 1;
         if (nb > tiles[i] && tiles[i] > 0) nb = tiles[i];
         if ((int)blockIdx.x < off + nb + 1) { e = i; bid = (int)blockIdx.x - off; maxp = nb; found = true; }
@@ -174,7 +178,7 @@ __global__ void __launch_bounds__(PART_THREADS, PART_BLOCKS_PER_SM + 1) k_partit
   }
   const unsigned epoch = c->part_epoch[e] + 1u;  // every block of the item reads these before it publishes; the item's
   const unsigned bar_base = c->bar_base[e];      // control block updates them after all of them have arrived
-  const DevLeaf L = V.leaves[leaf];
+  const DevLeaf L = mode == 0 ? c->item_rec[e] : V.leaves[leaf];
   const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
   const int ntiles = (L.count + PART_TILE - 1) / PART_TILE;
   // an empty leaf (possible on one rank of a data-parallel run: none of a globally splittable leaf's rows live in this
@@ -195,7 +199,7 @@ __global__ void __launch_bounds__(PART_THREADS, PART_BLOCKS_PER_SM + 1) k_partit
   int row0[PART_REPS];  // rows of the block's first tile stay in registers for the scatter
   PSTAGE(0);
   if (!control) {
-    const DevFeat F = V.feats[feature];
+    const DevFeat F = mode == 0 ? c->item_feat[e] : V.feats[feature];
     const SplitRule rule = make_rule(F, threshold, default_left);
     // The split feature is read from the column-major copy, whatever the size of the leaf: a 32-byte sector there holds
     // this feature of 32 neighbouring rows (several of them in the leaf when it is large), a sector of the row-major

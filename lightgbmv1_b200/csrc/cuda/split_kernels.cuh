@@ -883,6 +883,23 @@ __device__ void plan_commits(const DevView& V, int lane, CtrlShared& C) {
   if (lane == 0) { C.nc = nc; C.done = done; C.nl = nl; }
 }
 
+// Last act of the control step (all threads of the block, after the commits have been written): the leaf records and
+// split-feature descriptors of the next round's items go next to the item list, for k_partition's preamble.
+__device__ void publish_items(const DevView& V) {
+  DevCtl* c = V.ctl;
+  __threadfence_block();
+  __syncthreads();
+  if (c->done) return;
+  const int ni = c->num_items;
+  const int i = threadIdx.x >> 4, w = threadIdx.x & 15;   // 16 threads per item, one 4-byte word each per pass
+  if (i < ni && i < LGB_KMAX) {
+    const int leaf = c->item_leaf[i];
+    static_assert(sizeof(DevLeaf) / 4 <= 16 && sizeof(DevFeat) / 4 <= 16, "16 threads copy one item's records");
+    warp_copy_words(&c->item_rec[i], &V.leaves[leaf], (int)(sizeof(DevLeaf) / 4), w);
+    warp_copy_words(&c->item_feat[i], &V.feats[c->item_feature[i]], (int)(sizeof(DevFeat) / 4), w);
+  }
+}
+
 // mode 0: training.  grid = (num_features, 2 * LGB_KMAX): blockIdx.y = 2 * item + sel; sel 0 scans the smaller child of
 //         the item's leaf, sel 1 forms larger = parent - smaller and scans it.  Round 0: only (item 0, sel 0) = root.
 // mode 1: one explicit leaf of the leaf table (step-wise API / tests), grid = (num_features, 1); result -> best[leaf].
@@ -972,6 +989,7 @@ __global__ void __launch_bounds__(FS_THREADS, 4) k_find_split(DevView V, int mod
   const int nl0 = c->num_leaves, ns0 = c->num_splits;
   if (V.p.num_leaves > CTRL_MAX_LEAVES) {  // big trees: the general, sequential version
     if (warp == 0) commit_and_select_global(V, lane);
+    publish_items(V);
     return;
   }
   // step 2: stage every open leaf's key (and the children's keys of the expanded ones), let warp 0 decide the commits
@@ -989,12 +1007,24 @@ __global__ void __launch_bounds__(FS_THREADS, 4) k_find_split(DevView V, int mod
     const int l = threadIdx.x;  // FS_THREADS == CTRL_MAX_LEAVES
     const int mine = C.eligible[l];
     int rank = 0;
+    // only the eligible leaves are visited: their ballot words first (late in a tree a handful of 255 leaves)
+    __shared__ unsigned s_elig[FS_WARPS];
+    {
+      const unsigned w = __ballot_sync(FULL_MASK, mine != 0);
+      if (lane == 0) s_elig[warp] = w;
+    }
+    __syncthreads();
     if (mine) {
       const unsigned long long g = C.gk[l], t = C.tie[l];
-      const int nlf = C.nl;
-      for (int m = 0; m < nlf; ++m) {
-        const unsigned long long gm = C.gk[m], tm = C.tie[m];
-        rank += (C.eligible[m] && (gm > g || (gm == g && tm < t))) ? 1 : 0;
+#pragma unroll
+      for (int w = 0; w < FS_WARPS; ++w) {
+        unsigned bits = s_elig[w];
+        while (bits) {
+          const int m = 32 * w + __ffs(bits) - 1;
+          bits &= bits - 1;
+          const unsigned long long gm = C.gk[m], tm = C.tie[m];
+          rank += (gm > g || (gm == g && tm < t)) ? 1 : 0;
+        }
       }
       if (rank < K) {
         const int pd = C.pad[l];
@@ -1016,6 +1046,8 @@ __global__ void __launch_bounds__(FS_THREADS, 4) k_find_split(DevView V, int mod
   for (int i = warp; i < nc; i += FS_WARPS) commit_leaf_as(V, C.commit[i], nl0 + i, ns0 + i, lane);
   QSTAGE(4);
   if (threadIdx.x == 0) { c->num_leaves = nl0 + nc; c->num_splits = ns0 + nc; }
+  publish_items(V);
+  QSTAGE(5);
 #ifdef LGBCU_STAGE_TIMERS
   if (threadIdx.x == 0) { g_stage_cycles[6] += (unsigned long long)(clock64() - tc0); g_stage_cycles[7] += 1; }
 #endif
