@@ -1007,24 +1007,31 @@ __global__ void __launch_bounds__(FS_THREADS, 4) k_find_split(DevView V, int mod
     const int l = threadIdx.x;  // FS_THREADS == CTRL_MAX_LEAVES
     const int mine = C.eligible[l];
     int rank = 0;
-    // only the eligible leaves are visited: their ballot words first (late in a tree a handful of 255 leaves)
+    // the eligible leaves' keys are compacted first (late in a tree they are a handful of 255 leaves), so that the
+    // ranking loop is a dense, pipelined sweep
     __shared__ unsigned s_elig[FS_WARPS];
-    {
-      const unsigned w = __ballot_sync(FULL_MASK, mine != 0);
-      if (lane == 0) s_elig[warp] = w;
+    __shared__ unsigned long long s_gk[CTRL_MAX_LEAVES], s_tie[CTRL_MAX_LEAVES];
+    const unsigned long long g = C.gk[l], t = C.tie[l];
+    const unsigned eb = __ballot_sync(FULL_MASK, mine != 0);
+    if (lane == 0) s_elig[warp] = eb;
+    __syncthreads();
+    int n_el = 0, before = 0;
+#pragma unroll
+    for (int w = 0; w < FS_WARPS; ++w) {
+      const int pc = __popc(s_elig[w]);
+      before += w < warp ? pc : 0;
+      n_el += pc;
+    }
+    if (mine) {
+      const int pos = before + __popc(eb & ((1u << lane) - 1u));
+      s_gk[pos] = g; s_tie[pos] = t;
     }
     __syncthreads();
     if (mine) {
-      const unsigned long long g = C.gk[l], t = C.tie[l];
-#pragma unroll
-      for (int w = 0; w < FS_WARPS; ++w) {
-        unsigned bits = s_elig[w];
-        while (bits) {
-          const int m = 32 * w + __ffs(bits) - 1;
-          bits &= bits - 1;
-          const unsigned long long gm = C.gk[m], tm = C.tie[m];
-          rank += (gm > g || (gm == g && tm < t)) ? 1 : 0;
-        }
+#pragma unroll 4
+      for (int m = 0; m < n_el; ++m) {
+        const unsigned long long gm = s_gk[m], tm = s_tie[m];
+        rank += (gm > g || (gm == g && tm < t)) ? 1 : 0;
       }
       if (rank < K) {
         const int pd = C.pad[l];
@@ -1034,7 +1041,7 @@ __global__ void __launch_bounds__(FS_THREADS, 4) k_find_split(DevView V, int mod
         c->item_default_left[rank] = (pd >> (KEY_FEAT_BITS + 9)) & 1;
       }
     }
-    const int n_elig = __syncthreads_count(mine);
+    const int n_elig = n_el;
     if (threadIdx.x == 0) {
       c->num_items = n_elig < K ? n_elig : (K > 0 ? K : 0);
       c->round += 1;
