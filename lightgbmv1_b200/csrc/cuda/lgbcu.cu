@@ -158,6 +158,8 @@ struct LgbCuContext {
   int part_blocks_per_sm = PART_BLOCKS_PER_SM;  // lowered at create time if fewer k_partition blocks fit on an SM
   int hist_grid = 0;  // clusters that can be resident at once x HIST_CLUSTER
   bool force_dp_counts = false;  // LGBCU_FORCE_DP_COUNTS=1: single rank, but leaf counts as in data-parallel mode (tests)
+  std::vector<cudaGraphExec_t> chunk_graphs;  // further rounds in chunks of TREE_CHUNK_ROUNDS, for trees that outgrow the first batch
+  int last_used_rounds = 0;                   // rounds the previous tree needed
   cudaGraphExec_t tree_graph = nullptr; bool use_graph = true; bool graph_comm = true;  // the per-tree launch sequence, captured once
   int objective = LGBCU_OBJ_NONE; double obj_p[3] = {0, 0, 0};
   int root_count = 0; bool tree_begun = false;
@@ -202,6 +204,8 @@ int host_copy_threads(const LgbCuContext* c) {
 
 void drop_graph(LgbCuContext* c) {
   if (c->tree_graph) { cudaGraphExecDestroy(c->tree_graph); c->tree_graph = nullptr; }
+  for (cudaGraphExec_t g : c->chunk_graphs) if (g) cudaGraphExecDestroy(g);
+  c->chunk_graphs.clear();
 }
 
 int ensure_tree_buffers(LgbCuContext* c) {
@@ -964,6 +968,7 @@ int lgbcu_get_leaf_sums(LgbCuContext* c, int32_t leaf, double* sum_g, double* su
 
 // One round of tree growth = {k_hist, [all-reduce], k_find_split (+ control), k_partition}.  Round 0 handles the root;
 // every later round expands up to K leaves and commits at least one (see DevSpec in dev_types.cuh).
+#define TREE_CHUNK_ROUNDS 16
 static int enqueue_round(LgbCuContext* c, int round, cudaEvent_t* ev) {
   const DevView V = c->view();
   const int K = c->lookahead;
@@ -1003,24 +1008,42 @@ int lgbcu_train_tree(LgbCuContext* c, LgbCuSplitRecord* records, int32_t* num_sp
     c->ev.resize(EV * max_rounds);
     for (size_t i = old; i < c->ev.size(); ++i) CU(cudaEventCreate(&c->ev[i]));
   }
-  if (c->use_graph && !prof && (!c->comm || c->graph_comm)) {
-    // the launch sequence of a batch of rounds is fixed (all sizes are read on the device): capture once, replay per tree
-    if (!c->tree_graph) {
-      cudaGraph_t g = nullptr;
-      CU(cudaStreamBeginCapture(c->stream, cudaStreamCaptureModeThreadLocal));
-      const long long before = g_launches.load(std::memory_order_relaxed);  // captured launches are not executions
-      bool ok = true;
-      for (int r = 0; r < first_batch && ok; ++r) ok = enqueue_round(c, r, nullptr) == 0;
-      cudaError_t ce = cudaStreamEndCapture(c->stream, &g);
-      g_launches.fetch_add(before - g_launches.load(std::memory_order_relaxed), std::memory_order_relaxed);
-      if (!ok || ce != cudaSuccess || !g) { if (g) cudaGraphDestroy(g); return fail("lgbcu_train_tree: graph capture failed (%s)", cudaGetErrorString(ce)); }
-      ce = cudaGraphInstantiate(&c->tree_graph, g, 0);
-      cudaGraphDestroy(g);
-      if (ce != cudaSuccess) { c->tree_graph = nullptr; return fail("lgbcu_train_tree: graph instantiate failed (%s)", cudaGetErrorString(ce)); }
-    }
+  const bool graphs = c->use_graph && !prof && (!c->comm || c->graph_comm);
+  // the launch sequence of a range of rounds is fixed (all sizes are read on the device): capture once, replay per tree
+  auto capture_rounds = [&](int r0, int r1, cudaGraphExec_t* out) -> int {
+    cudaGraph_t g = nullptr;
+    CU(cudaStreamBeginCapture(c->stream, cudaStreamCaptureModeThreadLocal));
+    const long long before = g_launches.load(std::memory_order_relaxed);  // captured launches are not executions
+    bool ok = true;
+    for (int r = r0; r < r1 && ok; ++r) ok = enqueue_round(c, r, nullptr) == 0;
+    cudaError_t ce = cudaStreamEndCapture(c->stream, &g);
+    g_launches.fetch_add(before - g_launches.load(std::memory_order_relaxed), std::memory_order_relaxed);
+    if (!ok || ce != cudaSuccess || !g) { if (g) cudaGraphDestroy(g); return fail("lgbcu_train_tree: graph capture failed (%s)", cudaGetErrorString(ce)); }
+    ce = cudaGraphInstantiate(out, g, 0);
+    cudaGraphDestroy(g);
+    if (ce != cudaSuccess) { *out = nullptr; return fail("lgbcu_train_tree: graph instantiate failed (%s)", cudaGetErrorString(ce)); }
+    return 0;
+  };
+  // rounds [first_batch + j * TREE_CHUNK_ROUNDS, ...) as one more graph launch
+  auto launch_chunk = [&]() -> int {
+    const int j = (round - first_batch) / TREE_CHUNK_ROUNDS;
+    const int r1 = std::min(max_rounds, round + TREE_CHUNK_ROUNDS);
+    if ((int)c->chunk_graphs.size() <= j) c->chunk_graphs.resize((size_t)j + 1, nullptr);
+    if (!c->chunk_graphs[j] && capture_rounds(round, r1, &c->chunk_graphs[j])) return -1;
+    CU(cudaGraphLaunch(c->chunk_graphs[j], c->stream));
+    g_launches.fetch_add((long long)(r1 - round) * 3, std::memory_order_relaxed);
+    round = r1;
+    return 0;
+  };
+  if (graphs) {
+    if (!c->tree_graph && capture_rounds(0, first_batch, &c->tree_graph)) return -1;
     CU(cudaGraphLaunch(c->tree_graph, c->stream));
     g_launches.fetch_add((long long)first_batch * 3 + 1, std::memory_order_relaxed);
     round = first_batch;
+    // Late in a long run the trees are deep and need several times the first batch: enqueue what the previous tree
+    // needed before looking at `done` at all (a round enqueued after the tree is finished costs three empty launches)
+    while (round < max_rounds && round < c->last_used_rounds + 2)
+      if (launch_chunk()) return -1;
   } else {
     for (; round < first_batch; ++round)
       if (enqueue_round(c, round, prof ? &c->ev[EV * round] : nullptr)) return -1;
@@ -1031,9 +1054,14 @@ int lgbcu_train_tree(LgbCuContext* c, LgbCuSplitRecord* records, int32_t* num_sp
     CU(cudaMemcpyAsync(c->h_ctl, c->d_ctl, sizeof(DevCtl), cudaMemcpyDeviceToHost, c->stream));
     CU(cudaStreamSynchronize(c->stream));
     if (c->h_ctl->done || round >= max_rounds) break;
-    for (int i = 0; i < 8 && round < max_rounds; ++i, ++round)
-      if (enqueue_round(c, round, prof ? &c->ev[EV * round] : nullptr)) return -1;
+    if (graphs) {
+      if (launch_chunk()) return -1;
+    } else {
+      for (int i = 0; i < 8 && round < max_rounds; ++i, ++round)
+        if (enqueue_round(c, round, prof ? &c->ev[EV * round] : nullptr)) return -1;
+    }
   }
+  c->last_used_rounds = c->h_ctl->round;
   NEED(c->h_ctl->done, "lgbcu_train_tree: tree not finished after %d rounds", round);
   const int n = c->h_ctl->num_splits;
   NEED(n >= 0 && n <= L - 1, "lgbcu_train_tree: corrupt split count %d", n);
