@@ -166,6 +166,33 @@ __device__ __forceinline__ void chain1(const double* __restrict__ h, double* oh,
   }
   *ah_io = ah;
 }
+// The same walk over an input that was laid out in chain order beforehand (zero for skipped entries, zero padded by
+// CHAIN_PAD): no bounds or skip tests in the loop, 16-byte loads, and the next eight operands are fetched before the
+// current eight are added, so that the dependent DADDs are all the thread waits for.  Step i writes out0[DIR * i].
+template <int DIR>
+__device__ __forceinline__ void chain_lin(const double* __restrict__ in, double* out0, int count, double* ah_io) {
+  double ah = *ah_io;
+  const double2* in2 = reinterpret_cast<const double2*>(in);
+  double2 a = in2[0], b = in2[1], c = in2[2], d = in2[3];
+  int i = 0;
+  for (; i + 8 <= count; i += 8) {
+    const double2 na = in2[(i >> 1) + 4], nb = in2[(i >> 1) + 5], nc = in2[(i >> 1) + 6], nd = in2[(i >> 1) + 7];
+    ah += a.x; out0[DIR * (i + 0)] = ah;
+    ah += a.y; out0[DIR * (i + 1)] = ah;
+    ah += b.x; out0[DIR * (i + 2)] = ah;
+    ah += b.y; out0[DIR * (i + 3)] = ah;
+    ah += c.x; out0[DIR * (i + 4)] = ah;
+    ah += c.y; out0[DIR * (i + 5)] = ah;
+    ah += d.x; out0[DIR * (i + 6)] = ah;
+    ah += d.y; out0[DIR * (i + 7)] = ah;
+    a = na; b = nb; c = nc; d = nd;
+  }
+  const double v[8] = {a.x, a.y, b.x, b.y, c.x, c.y, d.x, d.y};
+#pragma unroll
+  for (int k = 0; k < 8; ++k)
+    if (i + k < count) { ah += v[k]; out0[DIR * (i + k)] = ah; }
+  *ah_io = ah;
+}
 template <int DIR>
 __device__ __forceinline__ void chain_cnt(const int* __restrict__ c, int* out, int t_first, int t_last, int skip_t,
                                           int sign, int* acc_io) {
@@ -197,8 +224,10 @@ __device__ __forceinline__ int key_pack(int feature, int threshold, int default_
 #define FS_WARPS (FS_THREADS / 32)
 
 // Shared-memory work area of one (feature, leaf) block.
-struct ScanSmem {
-  double gd[256], hd[256];      // data_[t] as doubles (after FixHistogram)
+#define CHAIN_PAD 16
+struct __align__(16) ScanSmem {
+  double cr[256 + CHAIN_PAD], cf[256 + CHAIN_PAD];  // inputs of the reverse / forward hessian chain, in chain order, zero padded
+  double hd[256];               // hessian data_[t] as doubles (after FixHistogram)
   i64 gi[256];                  // gradient entries in fixed point (exact prefix / suffix sums)
   i64 wtot[6][FS_WARPS];        // per-warp totals of the integer scans / reductions (one row per scan)
   double RG[256], RH[256];      // reverse scan: sum_right_gradient / sum_right_hessian after adding bin t
@@ -303,9 +332,17 @@ __device__ void scan_feature_block(ScanSmem& S, int nt, const DevFeat& F, double
   // the additions matters) are replayed sequentially by one thread each.  Warps 4..7: everything that is exact in
   // integers -- gradient sums (64-bit fixed point, rounded once) and the reconstructed counts -- as 128-thread
   // prefix / suffix scans over the <= 256 bins, two adjacent bins per thread, synchronised on named barrier 1.
+  const int cnt_r = t_hi - t_lo + 1;
+  for (int i = tid; i < 256 + CHAIN_PAD; i += FS_THREADS) {
+    const int t = t_hi - i;
+    S.cr[i] = (i < cnt_r && t != skip_t) ? S.hd[t] : 0.0;
+    S.cf[i] = (two_way && i <= t_end && i != skip_t) ? S.hd[i] : 0.0;
+  }
+  __syncthreads();
   if (tid == 0) {  // reverse hessian chain
     double ah = LGB_EPS;
-    chain1<-1>(S.hd, S.RH, t_hi, t_lo, skip_t, 1.0, &ah);
+    chain_lin<-1>(S.cr, &S.RH[t_hi], cnt_r, &ah);
+
   } else if (tid == 32 && two_way) {  // forward hessian chain
     double lh = LGB_EPS;
     if (implicit_first) {
@@ -313,8 +350,9 @@ __device__ void scan_feature_block(ScanSmem& S, int nt, const DevFeat& F, double
       chain1<1>(S.hd, nullptr, 0, nt - 1, -1000, -1.0, &lh);
     }
     S.base_h = lh;
-    chain1<1>(S.hd, S.LH, 0, t_end, skip_t, 1.0, &lh);
+    chain_lin<1>(S.cf, &S.LH[0], t_end + 1, &lh);
   } else if (warp >= FS_WARPS / 2) {
+    {
     const int j = tid - FS_THREADS / 2;
     const int e0 = 2 * j, e1 = 2 * j + 1;
     const i64 g0 = S.gi[e0], g1 = S.gi[e1];
@@ -341,6 +379,7 @@ __device__ void scan_feature_block(ScanSmem& S, int nt, const DevFeat& F, double
       group_scan_i64<1>(f0 ? c0 : 0, f1 ? c1 : 0, &a0, &a1, S.wtot[5], j);
       S.LC[e0] = (int)(base_c + a0); S.LC[e1] = (int)(base_c + a1);
       if (j == 0) { S.base_g = base_g; S.base_c = (int)base_c; }
+    }
     }
   }
   __syncthreads();
@@ -395,7 +434,7 @@ __device__ void scan_feature_block(ScanSmem& S, int nt, const DevFeat& F, double
       fb = cand_better(fb, c, false);
     }
   }
-  STAGE(20);
+  STAGE(24);
   rb = warp_best_cand(rb, true);
   fb = warp_best_cand(fb, false);
   splittable = __any_sync(FULL_MASK, splittable);
@@ -411,7 +450,7 @@ __device__ void scan_feature_block(ScanSmem& S, int nt, const DevFeat& F, double
     fb = warp_best_cand(y, false);
     splittable = __any_sync(FULL_MASK, sp);
   }
-  STAGE(21);
+  STAGE(25);
   if (tid != 0) return;
   const int any_split = splittable;
   // the winners' sums, formed exactly as the evaluating thread formed them
@@ -458,7 +497,7 @@ __device__ void scan_feature_block(ScanSmem& S, int nt, const DevFeat& F, double
   o.gain *= F.penalty;  // FindBestThreshold: output->gain *= meta_->penalty
   *out = o;
   *splittable_out = any_split;
-  STAGE(22);
+  STAGE(26);
 }
 
 // ComputeBestSplitForFeature (serial_tree_learner.cpp:709-718): the reference tests `leaf_index() == 0`, which holds
@@ -528,10 +567,9 @@ __device__ void find_item(const DevView& V, ScanSmem& S, int f, int sel, const F
             hs[1 + F.mfb] = e;
             *fix_s = make_double2(vg, vh);
           }
-          S.gd[tid] = tid == F.mfb ? vg : (double)e.g * inv_g;
           S.hd[tid] = tid == F.mfb ? vh : (double)e.h * inv_h;
         } else {
-          S.gd[tid] = (double)e.g * inv_g; S.hd[tid] = (double)e.h * inv_h;
+          S.hd[tid] = (double)e.h * inv_h;
         }
         S.gi[tid] = e.g;
         __syncthreads();
@@ -573,10 +611,9 @@ __device__ void find_item(const DevView& V, ScanSmem& S, int f, int sel, const F
           const double lg = pf.x - sg_fix, lh = pf.y - sh_fix;
           __syncthreads();  // every thread has read *fix_l
           if (tid == F.mfb) *fix_l = make_double2(lg, lh);
-          S.gd[tid] = tid == F.mfb ? lg : (double)e.g * inv_g;
           S.hd[tid] = tid == F.mfb ? lh : (double)e.h * inv_h;
         } else {
-          S.gd[tid] = (double)e.g * inv_g; S.hd[tid] = (double)e.h * inv_h;
+          S.hd[tid] = (double)e.h * inv_h;
         }
         S.gi[tid] = e.g;
         __syncthreads();
@@ -633,21 +670,22 @@ __device__ __forceinline__ void store_none_split(DevSplit* d, int lane) {
 struct PairBest { double gain; int real_feature, idx, pad; };
 
 // one warp: best (gain, feature) of row `p` of feat_key over all features; result in every lane (idx < 0: none)
-__device__ PairBest warp_reduce_feature_keys(const DevView& V, int p, int lane) {
+__device__ PairBest warp_reduce_feature_keys(const DevView& V, int p, int lane, int f_begin = 0, int f_end = -1) {
   const int F = V.num_features;
+  if (f_end < 0) f_end = F;
   double bg = LGB_MIN_SCORE; int bf = -1, bi = -1, bp = 0;
-  for (int j0 = lane; j0 < F; j0 += 4 * 32) {
+  for (int j0 = f_begin + lane; j0 < f_end; j0 += 4 * 32) {
     SplitKey k[4];
 #pragma unroll
     for (int u = 0; u < 4; ++u) {
       const int j = j0 + u * 32;
       k[u] = none_key();
-      if (j < F) k[u] = load_key_cg(&V.feat_key[(size_t)p * F + j]);
+      if (j < f_end) k[u] = load_key_cg(&V.feat_key[(size_t)p * F + j]);
     }
 #pragma unroll
     for (int u = 0; u < 4; ++u) {
       const int j = j0 + u * 32;
-      if (j < F && (bi < 0 || split_better(k[u].gain, k[u].real_feature, bg, bf))) {
+      if (j < f_end && (bi < 0 || split_better(k[u].gain, k[u].real_feature, bg, bf))) {
         bg = k[u].gain; bf = k[u].real_feature; bp = k[u].pad; bi = j;
       }
     }
@@ -966,6 +1004,38 @@ __global__ void __launch_bounds__(FS_THREADS, 4) k_find_split(DevView V, int mod
       store_leaf_best(V, 0, b, &V.best[leaf], &V.leaf_key[leaf], lane);
     }
   } else {
+    // Wide data with few items (K is small there): several warps share a row of feat_key, a slice of the features
+    // each, and the row's first warp combines their winners in slice order -- the same total order (gain, then the
+    // smaller real feature, then the earlier feature), so the same winner.
+    int wpr = 1;
+    if (V.num_features > 256) { while (wpr * 2 * (2 * ni) <= FS_WARPS) wpr *= 2; }
+    if (wpr > 1) {
+      __shared__ PairBest s_part[FS_WARPS];
+      const int p = warp / wpr, sl = warp % wpr;
+      DevSpec* sp = p < 2 * ni ? &V.spec[c->item_leaf[p >> 1]] : nullptr;
+      const bool live = sp && !sp->skip_find;
+      if (live) {
+        const int per = (V.num_features + wpr - 1) / wpr;
+        const int f0 = sl * per, f1 = min(V.num_features, f0 + per);
+        const PairBest b = warp_reduce_feature_keys(V, p, lane, f0, f1);
+        if (lane == 0) s_part[warp] = b;
+      }
+      __syncthreads();
+      if (sp && sl == 0) {
+        const int child = (p & 1) == 0 ? sp->smaller : 1 - sp->smaller;
+        if (!live) {
+          store_none_split(&sp->best[child], lane);
+          if (lane == 0) store_key(&sp->key[child], none_key());
+        } else {
+          PairBest b = s_part[warp];
+          for (int k = 1; k < wpr; ++k) {
+            const PairBest o = s_part[warp + k];
+            if (o.idx >= 0 && o.gain == o.gain && (b.idx < 0 || b.gain != b.gain || split_better(o.gain, o.real_feature, b.gain, b.real_feature))) b = o;
+          }
+          store_leaf_best(V, p, b, &sp->best[child], &sp->key[child], lane);
+        }
+      }
+    } else
     for (int p = warp; p < 2 * ni; p += FS_WARPS) {
       const int i = p >> 1, which = p & 1;  // which = 0: the smaller child's row, 1: the larger child's
       DevSpec* sp = &V.spec[c->item_leaf[i]];

@@ -10,9 +10,13 @@ import capi, workloads as W
 skip = int(sys.argv[1]) if len(sys.argv) > 1 else 470
 rows = int(sys.argv[2]) if len(sys.argv) > 2 else 10_500_000
 ours = capi.ours(); lib = ours.lib
-X, y = W.higgs_shaped(rows)
-ds = ours.dataset_from_mat(X, W.HIGGS_PARAMS + " num_threads=16"); ours.set_field(ds, "label", y)
-b = ours.booster_create(ds, W.HIGGS_PARAMS)
+shape = sys.argv[3] if len(sys.argv) > 3 else "higgs"
+if shape == "epsilon":
+    X, y = W.epsilon_shaped(rows if len(sys.argv) > 2 else 400_000, 2000); PARAMS = W.EPSILON_PARAMS
+else:
+    X, y = W.higgs_shaped(rows); PARAMS = W.HIGGS_PARAMS
+ds = ours.dataset_from_mat(X, PARAMS + " num_threads=16"); ours.set_field(ds, "label", y)
+b = ours.booster_create(ds, PARAMS)
 for _ in range(skip): ours.update(b)
 NR = 1024
 st = (C.c_ulonglong * (6 * NR))()
@@ -26,11 +30,12 @@ for rep in range(3):
     a = a[:used]
     hist = a[:, 1] - a[:, 0]; find = a[:, 2] - a[:, 1]; part = a[1:, 0] - a[:-1, 2]
     ok = (a[:, 2] > 0)
-    print(f"tree {skip + rep}: rounds {used}; span {(a[-1, 1] - a[0, 0]) / 1e6:.3f} ms; per round us  median hist {np.median(hist[ok]) / 1e3:.2f} "
+    if used > 2 and ok.sum() > 1: print(f"tree {skip + rep}: rounds {used}; span {(a[-1, 1] - a[0, 0]) / 1e6:.3f} ms; per round us  median hist {np.median(hist[ok]) / 1e3:.2f} "
           f"find {np.median(find[ok]) / 1e3:.2f} part {np.median(part[ok[:-1]]) / 1e3:.2f} | p10 {np.percentile(hist[ok], 10) / 1e3:.2f} "
           f"{np.percentile(find[ok], 10) / 1e3:.2f} {np.percentile(part[ok[:-1]], 10) / 1e3:.2f} | sum ms {hist[ok].sum() / 1e6:.2f} {find[ok].sum() / 1e6:.2f} {part[ok[:-1]].sum() / 1e6:.2f}")
     f = np.array(list(fs), dtype=np.float64) / 1.9e3 / used
     h = np.array(list(hs), dtype=np.float64) / 1.9e3 / used
     print("  find block(0,1) us/round: setup %.2f | find_item %.2f | ticket %.2f ; control total %.2f = reduce %.2f load %.2f plan %.2f items %.2f commit %.2f"
           % (f[0], f[1] + f[2] + f[3] + f[4], f[5], f[6], f[16], f[17], f[18], f[19], f[20]))
+    print("  find_item stages us/round [1,2,3,4 | 24,25,26]:", np.round(f[1:5], 2), np.round(f[24:27], 2))
     print("  part block 0 us/round:", np.round(f[8:13], 2), "  hist block 0 us/round [zero+prefetch, rows, sync, flush, sync, preamble]:", np.round(h[:6], 2))
