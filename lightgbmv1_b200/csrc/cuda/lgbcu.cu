@@ -213,10 +213,10 @@ int ensure_tree_buffers(LgbCuContext* c) {
   NEED(c->params_set, "lgbcu: tree params not set");
   const int L = c->params.num_leaves;
   // K leaves expanded per round.  Every expanded leaf costs 2 x F blocks in the split search of its round whether or
-  // not its turn comes soon, so wide data gets a smaller K: about two resident waves of search blocks per round
-  // (measured best on 28-, 137- and 2000-feature shapes: K = 16, 4, 1).
+  // not its turn comes soon, so very wide data gets a smaller K (measured in round 2, ms per iteration: 137 features
+  // K = 4 / 8 / 16 -> 9.6 / 8.8 / 8.3; 2000 features K = 1 / 2 / 4 -> 29.3 / 27.9 / 28.1; 28 features best at 16).
   int K = c->lookahead_cfg;
-  if (K <= 0) { K = c->num_sms * 4 / std::max(1, c->F); if (K < 1) K = 1; if (K > LGB_KMAX) K = LGB_KMAX; }
+  if (K <= 0) { K = c->num_sms * 16 / std::max(1, c->F); if (K < 2) K = 2; if (K > LGB_KMAX) K = LGB_KMAX; }
   if (c->alloc_leaves == L && c->alloc_lookahead == K && c->d_pool) return 0;
   c->lookahead = K;  // the memory guard below may lower it; alloc_lookahead remembers what was asked for
   drop_graph(c);
