@@ -204,6 +204,17 @@ LGBCU_API int lgbcu_bagging_reset(LgbCuContext* ctx, int32_t seed);
 LGBCU_API int lgbcu_bagging(LgbCuContext* ctx, double fraction, int32_t* bag_count);
 LGBCU_API int lgbcu_copy_bag(LgbCuContext* ctx, int32_t* out, int32_t n);
 
+/* GOSS (replaces the device-visible half of GOSS::BaggingHelper / GOSS::Bagging, src/boosting/goss.hpp:103-177).  The
+ * per-row decision depends on how many rows of the same thread chunk were sampled before it, so the walk stays on the
+ * host; the device hands out |gradient * hessian| per row (float, formed as the reference forms it) ...            */
+LGBCU_API int lgbcu_goss_scores(LgbCuContext* ctx, float* out_host, int32_t n);
+/* ... and applies the outcome: bit r of word r/32 of `inbag_bits` = row r is in the bag, of `amplify_bits` = row r is a
+ * sampled small-gradient row whose gradient and hessian are multiplied by chunk_multiply[r / chunk_rows].  The bag
+ * (in-bag rows ascending, then the others) is built on the device like lgbcu_bagging's; both bit arrays hold
+ * ceil(n / 1024) * 32 words.  Needs lgbcu_bagging_reset first.                                                       */
+LGBCU_API int lgbcu_goss_apply(LgbCuContext* ctx, const uint32_t* inbag_bits, const uint32_t* amplify_bits, int32_t chunk_rows,
+                               const float* chunk_multiply, int32_t nchunks, int32_t* bag_count);
+
 /* A8: BeforeTrain (src/treelearner/serial_tree_learner.cpp:244-272): reset partition / leaf table / pool,
  * root sums.  bag_indices==NULL -> all rows; feature_used==NULL -> all features (ColSampler by-tree mask). */
 LGBCU_API int lgbcu_begin_tree(LgbCuContext* ctx, const int32_t* bag_indices, int32_t bag_count,

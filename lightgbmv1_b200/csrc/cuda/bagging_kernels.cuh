@@ -65,7 +65,79 @@ __global__ void __launch_bounds__(256) k_bag_scatter(int n, const unsigned* __re
   }
 }
 
+// ---- GOSS (src/boosting/goss.hpp:103-152) -----------------------------------------------------------------------
+// The sampling decision of a row depends on how many rows of its thread chunk were sampled before it -- a sequential
+// walk per chunk -- so it stays on the host (gbdt.cpp GossSample).  The device supplies |g * h| per row in float, as
+// BaggingHelper forms it, and afterwards applies the result: two bit rows per 1024-row block (in the bag / sampled
+// small-gradient row whose gradient and hessian are scaled by its chunk's multiplier), from which the same scan +
+// stable scatter as plain bagging builds the bag.
+__global__ void k_goss_scores(int n, const float* __restrict__ g, const float* __restrict__ h, float* __restrict__ out) {
+  for (int i = blockIdx.x * blockDim.x + threadIdx.x; i < n; i += gridDim.x * blockDim.x) out[i] = fabsf(g[i] * h[i]);
+}
+
+// one 1024-thread block per 1024-row block: thread = row
+__global__ void __launch_bounds__(BAG_BLOCK) k_goss_apply(int n, const unsigned* __restrict__ bits, const unsigned* __restrict__ amp,
+                                                         int chunk_rows, const float* __restrict__ chunk_mult,
+                                                         float* __restrict__ g, float* __restrict__ h, int* __restrict__ tile_left) {
+  const int nblock = (n + BAG_BLOCK - 1) / BAG_BLOCK;
+  for (int b = blockIdx.x; b < nblock; b += gridDim.x) {
+    const int t = threadIdx.x, row = b * BAG_BLOCK + t;
+    const unsigned aw = amp[(size_t)b * 32 + (t >> 5)];
+    if (row < n && ((aw >> (t & 31)) & 1u)) {
+      const float m = chunk_mult[row / chunk_rows];
+      g[row] *= m; h[row] *= m;
+    }
+    if (t < 32) {
+      int cnt = __popc(bits[(size_t)b * 32 + t]);
+      for (int o = 16; o > 0; o >>= 1) cnt += __shfl_xor_sync(0xffffffffu, cnt, o);
+      if (t == 0) tile_left[b] = cnt;
+    }
+  }
+}
+
 extern "C" {
+
+int lgbcu_goss_scores(LgbCuContext* c, float* out, int32_t n) {
+  NEED(c && out && n == c->N && c->d_grad && c->d_hess, "lgbcu_goss_scores: bad argument / no gradients");
+  CU(cudaSetDevice(c->device));
+  if (!c->d_goss) CU(dev_alloc(&c->d_goss, (size_t)c->N));
+  LAUNCH(k_goss_scores, grid_for(c, c->N, 256), 256, 0, c->stream, c->N, c->d_grad, c->d_hess, c->d_goss);
+  CU(cudaGetLastError());
+  // straight into the caller's buffer (pinned or pageable); rows are spread over the copy threads by the caller's walk
+  CU(cudaMemcpyAsync(out, c->d_goss, sizeof(float) * (size_t)n, cudaMemcpyDeviceToHost, c->stream));
+  CU(cudaStreamSynchronize(c->stream));
+  return 0;
+}
+
+int lgbcu_goss_apply(LgbCuContext* c, const uint32_t* inbag_bits, const uint32_t* amplify_bits, int32_t chunk_rows,
+                     const float* chunk_multiply, int32_t nchunks, int32_t* bag_count) {
+  NEED(c && inbag_bits && amplify_bits && chunk_multiply && bag_count && chunk_rows > 0 && nchunks > 0, "lgbcu_goss_apply: bad argument");
+  NEED((long long)chunk_rows * nchunks >= c->N, "lgbcu_goss_apply: %d chunks of %d rows do not cover %d rows", nchunks, chunk_rows, c->N);
+  NEED(c->d_bag_state, "lgbcu_goss_apply: call lgbcu_bagging_reset first");
+  CU(cudaSetDevice(c->device));
+  const int nblock = (c->N + BAG_BLOCK - 1) / BAG_BLOCK;
+  if (!c->d_goss_amp) CU(dev_alloc(&c->d_goss_amp, (size_t)nblock * 32));
+  if (!c->d_goss_mult || c->goss_mult_cap < nchunks) {
+    if (c->d_goss_mult) { cudaFree(c->d_goss_mult); c->d_goss_mult = nullptr; }
+    CU(dev_alloc(&c->d_goss_mult, (size_t)nchunks));
+    c->goss_mult_cap = nchunks;
+  }
+  CU(cudaMemcpyAsync(c->d_bag_bits, inbag_bits, sizeof(unsigned) * (size_t)nblock * 32, cudaMemcpyHostToDevice, c->stream));
+  CU(cudaMemcpyAsync(c->d_goss_amp, amplify_bits, sizeof(unsigned) * (size_t)nblock * 32, cudaMemcpyHostToDevice, c->stream));
+  CU(cudaMemcpyAsync(c->d_goss_mult, chunk_multiply, sizeof(float) * (size_t)nchunks, cudaMemcpyHostToDevice, c->stream));
+  const int grid = grid_for(c, (long long)nblock * 32, 256);
+  LAUNCH(k_goss_apply, std::min(nblock, c->num_sms * 2), BAG_BLOCK, 0, c->stream, c->N, c->d_bag_bits, c->d_goss_amp, (int)chunk_rows,
+         c->d_goss_mult, c->d_grad, c->d_hess, c->d_bag_tile);
+  LAUNCH(k_na_scan, 1, 1024, 0, c->stream, c->d_bag_tile, c->N, c->d_bag_ctl, reinterpret_cast<int*>(c->d_bag_ctl + 1));
+  LAUNCH(k_bag_scatter, grid, 256, 0, c->stream, c->N, c->d_bag_bits, c->d_bag_tile, c->d_bag_ctl, c->d_bag);
+  CU(cudaGetLastError());
+  CU(cudaMemcpyAsync(c->h_ctl, c->d_bag_ctl, sizeof(unsigned), cudaMemcpyDeviceToHost, c->stream));
+  CU(cudaStreamSynchronize(c->stream));
+  c->bag_count = (int)*reinterpret_cast<unsigned*>(c->h_ctl);
+  c->bag_ready = true;
+  *bag_count = c->bag_count;
+  return 0;
+}
 
 int lgbcu_bagging_reset(LgbCuContext* c, int32_t seed) {
   NEED(c && c->N > 0, "lgbcu_bagging_reset: dataset not set");

@@ -119,6 +119,7 @@ struct LgbCuContext {
   uint8_t* d_bins_col = nullptr; long long col_stride = 0;
   // device-side bagging (bagging_kernels.cuh)
   unsigned* d_bag_state = nullptr; unsigned* d_bag_bits = nullptr; int* d_bag_tile = nullptr; unsigned* d_bag_ctl = nullptr;
+  float* d_goss = nullptr; unsigned* d_goss_amp = nullptr; float* d_goss_mult = nullptr; int goss_mult_cap = 0;  // GOSS: |g*h|, amplified-row bits, chunk multipliers
   int* d_bag = nullptr; int bag_count = 0; bool bag_ready = false;
   // query structure (lambdarank)
   int* d_query = nullptr; int num_queries = 0; int max_query = 0;
@@ -440,7 +441,7 @@ int lgbcu_destroy(LgbCuContext* c) {
                   c->d_inv_max_dcg, c->d_sigmoid_table, c->d_pool, c->d_splittable, c->d_leaves, c->d_best,
                   c->d_feat_best, c->d_ctl, c->d_records, c->d_leaf_value, c->d_export, c->d_tree_i32, c->d_tree_i8,
                   c->d_tree_f64, c->d_rows, c->d_scratch, c->d_parent_split, c->d_mfb_fix, c->d_feat_key, c->d_leaf_key, c->d_spec, c->d_expanded,
-                  c->d_bag_state, c->d_bag_bits, c->d_bag_tile, c->d_bag_ctl, c->d_bag};
+                  c->d_bag_state, c->d_bag_bits, c->d_bag_tile, c->d_bag_ctl, c->d_bag, c->d_goss, c->d_goss_amp, c->d_goss_mult};
   for (void* p : ptrs) if (p) cudaFree(p);
   if (c->h_records) cudaFreeHost(c->h_records);
   if (c->h_ctl) cudaFreeHost(c->h_ctl);

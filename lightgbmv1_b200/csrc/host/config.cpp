@@ -158,7 +158,8 @@ void Config::Set(const std::unordered_map<std::string, std::string>& p) {
   if (GetStr(p, "boosting", &s)) {
     std::transform(s.begin(), s.end(), s.begin(), ::tolower);
     if (s == "gbdt" || s == "gbrt") boosting = "gbdt";
-    else Log::Fatal("boosting=%s is outside this library's path (only gbdt is built)", s.c_str());
+    else if (s == "goss") boosting = "goss";
+    else Log::Fatal("boosting=%s is outside this library's path (gbdt and goss are built)", s.c_str());
   }
   if (GetStr(p, "objective", &s)) objective = ObjectiveAlias(s);
   // GetMetricType (src/io/config.cpp:87-100): lower-case, split on ',', ParseMetricAlias, drop repeats; with no
@@ -212,6 +213,10 @@ void Config::Set(const std::unordered_map<std::string, std::string>& p) {
   GetInt(p, "min_data_in_leaf", &min_data_in_leaf);
   GetDouble(p, "min_sum_hessian_in_leaf", &min_sum_hessian_in_leaf);
   GetDouble(p, "bagging_fraction", &bagging_fraction);
+  GetDouble(p, "top_rate", &top_rate);
+  GetDouble(p, "other_rate", &other_rate);
+  if (top_rate < 0.0 || top_rate > 1.0) Log::Fatal("top_rate should be in [0, 1]");
+  if (other_rate < 0.0 || other_rate > 1.0) Log::Fatal("other_rate should be in [0, 1]");
   GetDouble(p, "pos_bagging_fraction", &pos_bagging_fraction);
   GetDouble(p, "neg_bagging_fraction", &neg_bagging_fraction);
   GetInt(p, "bagging_freq", &bagging_freq);

@@ -30,6 +30,7 @@ struct Config {
   int min_data_in_leaf = 20;
   double min_sum_hessian_in_leaf = 1e-3;
   double bagging_fraction = 1.0;
+  double top_rate = 0.2, other_rate = 0.1;  // GOSS (config.h:399-405)
   double pos_bagging_fraction = 1.0, neg_bagging_fraction = 1.0;
   int bagging_freq = 0;
   int bagging_seed = 3;

@@ -6,6 +6,7 @@
 #include <omp.h>
 
 #include <algorithm>
+#include <functional>
 #include <cmath>
 #include <cstring>
 
@@ -111,8 +112,24 @@ GBDT::GBDT(const Dataset* train, const Config& config)
     metrics_.push_back(spec);
   }
 
+  // ---- GOSS::ResetGoss (goss.hpp:77-101)
+  is_goss_ = config_.boosting == "goss";
+  if (is_goss_) {
+    if (!(config_.top_rate + config_.other_rate <= 1.0)) Log::Fatal("Check failed: config_->top_rate + config_->other_rate <= 1.0f");
+    if (!(config_.top_rate > 0.0 && config_.other_rate > 0.0)) Log::Fatal("Check failed: config_->top_rate > 0.0f && config_->other_rate > 0.0f");
+    if (config_.bagging_freq > 0 && config_.bagging_fraction != 1.0) Log::Fatal("Cannot use bagging in GOSS");
+    Log::Info("Using GOSS");
+    const int nblock = (N + 1023) / 1024;
+    goss_rands_.clear();
+    for (int i = 0; i < nblock; ++i) goss_rands_.emplace_back(config_.bagging_seed + i);
+    goss_score_.resize(static_cast<size_t>(N));
+    goss_inbag_.assign(static_cast<size_t>(nblock) * 32, 0u);
+    goss_amp_.assign(static_cast<size_t>(nblock) * 32, 0u);
+    Check(lgbcu_bagging_reset(ctx_, config_.bagging_seed));  // allocates the device-side bag
+    bag_cnt_ = N;  // "flag to not bagging first"
+  }
   // ---- ResetBaggingConfig (gbdt.cpp:739-797)
-  if (config_.bagging_fraction < 1.0 && config_.bagging_freq > 0) {
+  if (!is_goss_ && config_.bagging_fraction < 1.0 && config_.bagging_freq > 0) {
     bag_cnt_ = static_cast<data_size_t>(config_.bagging_fraction * N);
     Check(lgbcu_bagging_reset(ctx_, config_.bagging_seed));  // one generator per 1024-row block, seeded bagging_seed + block
     use_bagging_ = true;
@@ -151,6 +168,7 @@ void GBDT::ResetFeatureMask() {
 // device and the bag stays there; the host only learns its size
 void GBDT::Bagging(int iter) {
   const int N = train_->num_data();
+  if (is_goss_) { GossSample(iter); return; }
   if (!use_bagging_) return;
   if (!((bag_cnt_ < N && config_.bagging_freq > 0 && iter % config_.bagging_freq == 0) || need_re_bagging_)) return;
   need_re_bagging_ = false;
@@ -158,6 +176,65 @@ void GBDT::Bagging(int iter) {
   Check(lgbcu_bagging(ctx_, config_.bagging_fraction, &cnt));
   bag_cnt_ = cnt;
   Log::Debug("Re-bagging, using %d data to train", bag_cnt_);
+}
+
+// GOSS::Bagging + GOSS::BaggingHelper (goss.hpp:103-177).  The walk over a chunk is sequential (the probability of
+// keeping a small-gradient row depends on how many were kept before it) and the chunks are the reference's: one per
+// thread, a multiple of 1024 rows (Threading::BlockInfoForceSize, threading.h:42-56), so like the reference the sample
+// depends on num_threads.  The device supplies |g * h| and applies the outcome (lgbcu_goss_scores / lgbcu_goss_apply).
+void GBDT::GossSample(int iter) {
+  const int N = train_->num_data();
+  bag_cnt_ = N;
+  if (iter < static_cast<int>(1.0f / config_.learning_rate)) return;  // not subsample for first iterations
+  Check(lgbcu_goss_scores(ctx_, goss_score_.data(), N));
+  const int num_threads = config_.num_threads > 0 ? config_.num_threads : omp_get_max_threads();
+  const int min_block = 1024;
+  int nblock = std::min<int>(num_threads, (N + min_block - 1) / min_block);
+  int inner = N;
+  if (nblock > 1) {
+    inner = (N + nblock - 1) / nblock;
+    inner = (inner + min_block - 1) / min_block * min_block;
+  }
+  std::fill(goss_inbag_.begin(), goss_inbag_.end(), 0u);
+  std::fill(goss_amp_.begin(), goss_amp_.end(), 0u);
+  std::vector<float> mult(static_cast<size_t>(nblock), 1.0f);
+  const float* score = goss_score_.data();
+#pragma omp parallel for schedule(static, 1) num_threads(num_threads)
+  for (int b = 0; b < nblock; ++b) {
+    const int start = b * inner;
+    const int cnt = std::min(inner, N - start);
+    if (cnt <= 0) continue;
+    int top_k = static_cast<int>(cnt * config_.top_rate);
+    const int other_k = static_cast<int>(cnt * config_.other_rate);
+    top_k = std::max(1, top_k);
+    // ArgMaxAtK(..., top_k - 1): the top_k-th largest value
+    std::vector<float> tmp(score + start, score + start + cnt);
+    std::nth_element(tmp.begin(), tmp.begin() + (top_k - 1), tmp.end(), std::greater<float>());
+    const float threshold = tmp[top_k - 1];
+    const float multiply = static_cast<float>(cnt - top_k) / other_k;
+    mult[b] = multiply;
+    int left = 0, big = 0;
+    for (int i = 0; i < cnt; ++i) {
+      const int idx = start + i;
+      bool in = false;
+      if (score[idx] >= threshold) {
+        in = true; ++big;
+      } else {
+        const int sampled = left - big;
+        const int rest_need = other_k - sampled;
+        const int rest_all = (cnt - i) - (top_k - big);
+        const double prob = rest_need / static_cast<double>(rest_all);
+        if (goss_rands_[idx / 1024].NextFloat() < prob) {
+          in = true;
+          goss_amp_[static_cast<size_t>(idx) >> 5] |= 1u << (idx & 31);  // chunks are multiples of 1024 rows: no word is shared
+        }
+      }
+      if (in) { ++left; goss_inbag_[static_cast<size_t>(idx) >> 5] |= 1u << (idx & 31); }
+    }
+  }
+  int32_t cnt = 0;
+  Check(lgbcu_goss_apply(ctx_, goss_inbag_.data(), goss_amp_.data(), inner, mult.data(), nblock, &cnt));
+  bag_cnt_ = cnt;
 }
 
 bool GBDT::TrainOneIter(const float* grad, const float* hess) {
@@ -189,7 +266,7 @@ bool GBDT::TrainOneIter(const float* grad, const float* hess) {
 
   std::unique_ptr<Tree> tree(new Tree(2));
   bool should_continue = false;
-  const bool bagged = use_bagging_ && bag_cnt_ < N;
+  const bool bagged = (use_bagging_ || is_goss_) && bag_cnt_ < N;
   if (class_need_train_) {
     ResetFeatureMask();  // BeforeTrain: col_sampler_.ResetByTree()
     Check(lgbcu_begin_tree(ctx_, bagged ? LGBCU_DEVICE_BAG : nullptr, bagged ? bag_cnt_ : 0,

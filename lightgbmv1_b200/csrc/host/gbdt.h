@@ -82,6 +82,12 @@ class GBDT {
   data_size_t bag_cnt_;     // the bag itself (in-bag rows ascending, then out-of-bag rows) lives on the device
   bool use_bagging_ = false;
   bool need_re_bagging_ = false;
+  // GOSS (goss.hpp): host-side sampling state
+  bool is_goss_ = false;
+  void GossSample(int iter);
+  std::vector<Random> goss_rands_;          // one generator per 1024-row block, seeded bagging_seed + block
+  std::vector<float> goss_score_;           // |g * h| per row, fetched from the device
+  std::vector<uint32_t> goss_inbag_, goss_amp_;
   // column sampling (col_sampler.hpp)
   Random feature_rand_;
   std::vector<int> valid_features_;  // real indices of used features
