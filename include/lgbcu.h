@@ -202,6 +202,9 @@ LGBCU_API int lgbcu_add_score_by_tree(LgbCuContext* ctx, int32_t num_leaves, con
 #define LGBCU_DEVICE_OOB ((const int32_t*)(intptr_t)-1)
 LGBCU_API int lgbcu_bagging_reset(LgbCuContext* ctx, int32_t seed);
 LGBCU_API int lgbcu_bagging(LgbCuContext* ctx, double fraction, int32_t* bag_count);
+/* the same draw with the fraction chosen by the row's label: > 0 -> pos_fraction, else neg_fraction (BalancedBaggingHelper,
+ * src/boosting/gbdt.cpp:183-207); needs the labels on the device (lgbcu_set_label) */
+LGBCU_API int lgbcu_bagging_balanced(LgbCuContext* ctx, double pos_fraction, double neg_fraction, int32_t* bag_count);
 LGBCU_API int lgbcu_copy_bag(LgbCuContext* ctx, int32_t* out, int32_t n);
 
 /* GOSS (replaces the device-visible half of GOSS::BaggingHelper / GOSS::Bagging, src/boosting/goss.hpp:103-177).  The

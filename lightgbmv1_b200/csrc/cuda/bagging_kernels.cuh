@@ -18,7 +18,10 @@ __global__ void k_bag_seed(int nblock, int seed, unsigned* __restrict__ state) {
 }
 
 // one warp per 1024-row block
-__global__ void __launch_bounds__(256) k_bag_flags(int n, double fraction, BagJump J, unsigned* __restrict__ state,
+// label == nullptr: every row is kept with probability `fraction`; otherwise rows with label > 0 with `fraction`, the
+// others with `fraction_neg` (BalancedBaggingHelper, gbdt.cpp:183-207)
+__global__ void __launch_bounds__(256) k_bag_flags(int n, double fraction, double fraction_neg, const float* __restrict__ label,
+                                                   BagJump J, unsigned* __restrict__ state,
                                                    unsigned* __restrict__ bits, int* __restrict__ tile_left) {
   const int lane = threadIdx.x & 31;
   const int nblock = (n + BAG_BLOCK - 1) / BAG_BLOCK;
@@ -31,7 +34,11 @@ __global__ void __launch_bounds__(256) k_bag_flags(int n, double fraction, BagJu
     for (int i = 0; i < 32; ++i) {
       x = 214013u * x + 2531011u;
       const float r = (float)((x >> 16) & 0x7FFFu) / 32768.0f;
-      if (row0 + i < n) { x_last = x; if ((double)r < fraction) word |= 1u << i; }
+      if (row0 + i < n) {
+        x_last = x;
+        const double fr = (label == nullptr || label[row0 + i] > 0.f) ? fraction : fraction_neg;
+        if ((double)r < fr) word |= 1u << i;
+      }
     }
     bits[(size_t)b * 32 + lane] = word;
     int cnt = __popc(word);
@@ -154,8 +161,20 @@ int lgbcu_bagging_reset(LgbCuContext* c, int32_t seed) {
   return 0;
 }
 
+static int bagging_draw(LgbCuContext* c, double fraction, double fraction_neg, const float* label, int32_t* bag_count);
+
 int lgbcu_bagging(LgbCuContext* c, double fraction, int32_t* bag_count) {
   NEED(c && bag_count, "lgbcu_bagging: NULL argument");
+  return bagging_draw(c, fraction, fraction, nullptr, bag_count);
+}
+
+int lgbcu_bagging_balanced(LgbCuContext* c, double pos_fraction, double neg_fraction, int32_t* bag_count) {
+  NEED(c && bag_count, "lgbcu_bagging_balanced: NULL argument");
+  NEED(c->d_label, "lgbcu_bagging_balanced: labels not set");
+  return bagging_draw(c, pos_fraction, neg_fraction, c->d_label, bag_count);
+}
+
+static int bagging_draw(LgbCuContext* c, double fraction, double fraction_neg, const float* label, int32_t* bag_count) {
   NEED(c->d_bag_state, "lgbcu_bagging: call lgbcu_bagging_reset first");
   CU(cudaSetDevice(c->device));
   BagJump J;
@@ -167,7 +186,7 @@ int lgbcu_bagging(LgbCuContext* c, double fraction, int32_t* bag_count) {
   }
   const int nblock = (c->N + BAG_BLOCK - 1) / BAG_BLOCK;
   const int grid = grid_for(c, (long long)nblock * 32, 256);
-  LAUNCH(k_bag_flags, grid, 256, 0, c->stream, c->N, fraction, J, c->d_bag_state, c->d_bag_bits, c->d_bag_tile);
+  LAUNCH(k_bag_flags, grid, 256, 0, c->stream, c->N, fraction, fraction_neg, label, J, c->d_bag_state, c->d_bag_bits, c->d_bag_tile);
   LAUNCH(k_na_scan, 1, 1024, 0, c->stream, c->d_bag_tile, c->N, c->d_bag_ctl, reinterpret_cast<int*>(c->d_bag_ctl + 1));
   LAUNCH(k_bag_scatter, grid, 256, 0, c->stream, c->N, c->d_bag_bits, c->d_bag_tile, c->d_bag_ctl, c->d_bag);
   CU(cudaGetLastError());

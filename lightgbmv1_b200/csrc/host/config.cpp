@@ -272,7 +272,8 @@ void Config::Set(const std::unordered_map<std::string, std::string>& p) {
   // options that would change the trees but are not built: refuse rather than silently differ
   if (extra_trees) Log::Fatal("extra_trees is outside this library's path");
   if (feature_fraction_bynode < 1.0) Log::Fatal("feature_fraction_bynode < 1 is outside this library's path");
-  if (pos_bagging_fraction < 1.0 || neg_bagging_fraction < 1.0) Log::Fatal("balanced bagging is outside this library's path");
+  if (pos_bagging_fraction <= 0.0 || pos_bagging_fraction > 1.0) Log::Fatal("pos_bagging_fraction should be in (0, 1]");
+  if (neg_bagging_fraction <= 0.0 || neg_bagging_fraction > 1.0) Log::Fatal("neg_bagging_fraction should be in (0, 1]");
   for (const char* k : {"monotone_constraints", "forcedsplits_filename", "forcedbins_filename", "interaction_constraints",
                         "cegb_penalty_feature_lazy", "cegb_penalty_feature_coupled", "max_bin_by_feature",
                         "categorical_feature", "linear_tree"}) {

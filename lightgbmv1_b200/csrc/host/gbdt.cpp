@@ -129,8 +129,16 @@ GBDT::GBDT(const Dataset* train, const Config& config)
     bag_cnt_ = N;  // "flag to not bagging first"
   }
   // ---- ResetBaggingConfig (gbdt.cpp:739-797)
-  if (!is_goss_ && config_.bagging_fraction < 1.0 && config_.bagging_freq > 0) {
-    bag_cnt_ = static_cast<data_size_t>(config_.bagging_fraction * N);
+  const data_size_t num_pos = objective_ ? objective_->NumPositiveData() : 0;
+  const bool balance_cond = (config_.pos_bagging_fraction < 1.0 || config_.neg_bagging_fraction < 1.0) && num_pos > 0;
+  if (!is_goss_ && (config_.bagging_fraction < 1.0 || balance_cond) && config_.bagging_freq > 0) {
+    if (balance_cond) {
+      balanced_bagging_ = true;
+      bag_cnt_ = static_cast<data_size_t>(num_pos * config_.pos_bagging_fraction) +
+                 static_cast<data_size_t>((N - num_pos) * config_.neg_bagging_fraction);
+    } else {
+      bag_cnt_ = static_cast<data_size_t>(config_.bagging_fraction * N);
+    }
     Check(lgbcu_bagging_reset(ctx_, config_.bagging_seed));  // one generator per 1024-row block, seeded bagging_seed + block
     use_bagging_ = true;
     need_re_bagging_ = true;
@@ -173,7 +181,8 @@ void GBDT::Bagging(int iter) {
   if (!((bag_cnt_ < N && config_.bagging_freq > 0 && iter % config_.bagging_freq == 0) || need_re_bagging_)) return;
   need_re_bagging_ = false;
   int32_t cnt = 0;
-  Check(lgbcu_bagging(ctx_, config_.bagging_fraction, &cnt));
+  if (balanced_bagging_) Check(lgbcu_bagging_balanced(ctx_, config_.pos_bagging_fraction, config_.neg_bagging_fraction, &cnt));
+  else Check(lgbcu_bagging(ctx_, config_.bagging_fraction, &cnt));
   bag_cnt_ = cnt;
   Log::Debug("Re-bagging, using %d data to train", bag_cnt_);
 }

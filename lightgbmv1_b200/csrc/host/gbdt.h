@@ -82,6 +82,7 @@ class GBDT {
   data_size_t bag_cnt_;     // the bag itself (in-bag rows ascending, then out-of-bag rows) lives on the device
   bool use_bagging_ = false;
   bool need_re_bagging_ = false;
+  bool balanced_bagging_ = false;  // pos_/neg_bagging_fraction by label (BalancedBaggingHelper, gbdt.cpp:183-207)
   // GOSS (goss.hpp): host-side sampling state
   bool is_goss_ = false;
   void GossSample(int iter);

@@ -16,6 +16,7 @@ class BinaryLogloss : public Objective {
     if (sigmoid_ <= 0.0) Log::Fatal("Sigmoid parameter %f should be greater than zero", sigmoid_);
     if (is_unbalance_ && std::fabs(scale_pos_weight_ - 1.0f) > 1e-6) Log::Fatal("Cannot set is_unbalance and scale_pos_weight at the same time");
   }
+  data_size_t NumPositiveData() const override { return num_pos_; }
   void Init(const Metadata& meta, data_size_t n, const SumSync& sum_over_ranks) override {
     num_data_ = n; label_ = meta.label.data(); weights_ = meta.weights.empty() ? nullptr : meta.weights.data();
     if (meta.label.empty()) Log::Fatal("Label should not be NULL");

@@ -24,6 +24,7 @@ class Objective {
   virtual void Configure(LgbCuContext* ctx) const = 0;  // push kind + parameters to the device learner
   virtual double BoostFromScore() const = 0;
   virtual bool NeedTrain() const { return true; }
+  virtual data_size_t NumPositiveData() const { return 0; }  // rows of this machine with label > 0 (balanced bagging)
   virtual bool IsConstantHessian() const { return false; }
   virtual void ConvertOutput(const double* in, double* out) const { out[0] = in[0]; }
   virtual std::string ToString() const = 0;

@@ -40,3 +40,17 @@ def test_goss_rejects_bagging_like_the_reference():
     with pytest.raises(Exception, match="Cannot use bagging in GOSS"):
         ours.booster_create(ds, BASE + " bagging_fraction=0.5 bagging_freq=1")
     ours.dataset_free(ds)
+
+
+@pytest.mark.parametrize("pos,neg,freq", [(0.5, 0.8, 2), (1.0, 0.3, 1), (0.25, 1.0, 3)])
+def test_balanced_bagging_identical_trees(pos, neg, freq):
+    """pos_/neg_bagging_fraction (GBDT::BalancedBaggingHelper, src/boosting/gbdt.cpp:183-207): the per-block generators
+    are the plain bagging ones, the fraction a row is tested against depends on its label."""
+    X, y = higgs_like(21, 40_000)
+    params = ("objective=binary num_leaves=31 learning_rate=0.1 min_data_in_leaf=20 min_sum_hessian_in_leaf=1e-3 "
+              f"verbosity=-1 pos_bagging_fraction={pos} neg_bagging_fraction={neg} bagging_freq={freq} bagging_seed=7")
+    ref, ours, br, bo, nr, no = run_both(X, y, params, 12)
+    assert nr == no == 12
+    assert_same_model(ref, ours, br, bo)
+    pr, po = ref.get_predict(br, len(y)), ours.get_predict(bo, len(y))
+    assert np.max(np.abs(pr - po)) <= 1e-9
