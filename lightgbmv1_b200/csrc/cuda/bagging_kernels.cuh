@@ -106,7 +106,7 @@ extern "C" {
 
 int lgbcu_goss_scores(LgbCuContext* c, float* out, int32_t n) {
   NEED(c && out && n == c->N && c->d_grad && c->d_hess, "lgbcu_goss_scores: bad argument / no gradients");
-  CU(cudaSetDevice(c->device));
+  USE_DEVICE(c->device);
   if (!c->d_goss) CU(dev_alloc(&c->d_goss, (size_t)c->N));
   LAUNCH(k_goss_scores, grid_for(c, c->N, 256), 256, 0, c->stream, c->N, c->d_grad, c->d_hess, c->d_goss);
   CU(cudaGetLastError());
@@ -121,7 +121,7 @@ int lgbcu_goss_apply(LgbCuContext* c, const uint32_t* inbag_bits, const uint32_t
   NEED(c && inbag_bits && amplify_bits && chunk_multiply && bag_count && chunk_rows > 0 && nchunks > 0, "lgbcu_goss_apply: bad argument");
   NEED((long long)chunk_rows * nchunks >= c->N, "lgbcu_goss_apply: %d chunks of %d rows do not cover %d rows", nchunks, chunk_rows, c->N);
   NEED(c->d_bag_state, "lgbcu_goss_apply: call lgbcu_bagging_reset first");
-  CU(cudaSetDevice(c->device));
+  USE_DEVICE(c->device);
   const int nblock = (c->N + BAG_BLOCK - 1) / BAG_BLOCK;
   if (!c->d_goss_amp) CU(dev_alloc(&c->d_goss_amp, (size_t)nblock * 32));
   if (!c->d_goss_mult || c->goss_mult_cap < nchunks) {
@@ -148,7 +148,7 @@ int lgbcu_goss_apply(LgbCuContext* c, const uint32_t* inbag_bits, const uint32_t
 
 int lgbcu_bagging_reset(LgbCuContext* c, int32_t seed) {
   NEED(c && c->N > 0, "lgbcu_bagging_reset: dataset not set");
-  CU(cudaSetDevice(c->device));
+  USE_DEVICE(c->device);
   const int nblock = (c->N + BAG_BLOCK - 1) / BAG_BLOCK;
   CU(dev_alloc(&c->d_bag_state, (size_t)nblock));
   CU(dev_alloc(&c->d_bag_bits, (size_t)nblock * 32));
@@ -176,7 +176,7 @@ int lgbcu_bagging_balanced(LgbCuContext* c, double pos_fraction, double neg_frac
 
 static int bagging_draw(LgbCuContext* c, double fraction, double fraction_neg, const float* label, int32_t* bag_count) {
   NEED(c->d_bag_state, "lgbcu_bagging: call lgbcu_bagging_reset first");
-  CU(cudaSetDevice(c->device));
+  USE_DEVICE(c->device);
   BagJump J;
   {  // affine maps of the LCG for 32 l steps, l = 0..31
     unsigned a32 = 1, c32 = 0;
@@ -200,7 +200,7 @@ static int bagging_draw(LgbCuContext* c, double fraction, double fraction_neg, c
 
 int lgbcu_copy_bag(LgbCuContext* c, int32_t* out, int32_t n) {
   NEED(c && out && n == c->N && c->bag_ready, "lgbcu_copy_bag: bad argument / no bag drawn");
-  CU(cudaSetDevice(c->device));
+  USE_DEVICE(c->device);
   CU(cudaMemcpyAsync(out, c->d_bag, sizeof(int) * (size_t)n, cudaMemcpyDeviceToHost, c->stream));
   CU(cudaStreamSynchronize(c->stream));
   return 0;

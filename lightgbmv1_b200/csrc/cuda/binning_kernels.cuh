@@ -48,7 +48,7 @@ extern "C" {
 
 int lgbcu_binned_free(LgbCuBinnedMatrix* m) {
   if (!m) return 0;
-  cudaSetDevice(m->device);
+  ScopedDevice dev_(m->device);
   if (m->d_bins) cudaFree(m->d_bins);
   delete m;
   return 0;
@@ -63,7 +63,7 @@ int lgbcu_bin_matrix(int device, const void* data, int data_type, int32_t nrow, 
   int ndev = 0;
   if (cudaGetDeviceCount(&ndev) != cudaSuccess || ndev == 0) { cudaGetLastError(); return fail("lgbcu_bin_matrix: no CUDA device available"); }
   NEED(device >= 0 && device < ndev, "lgbcu_bin_matrix: device %d out of range (have %d)", device, ndev);
-  CU(cudaSetDevice(device));
+  USE_DEVICE(device);
   struct Guard {   // everything but the result is released on every way out
     void* dev[4] = {nullptr, nullptr, nullptr, nullptr}; void* pin[2] = {nullptr, nullptr};
     cudaStream_t s[2] = {nullptr, nullptr}; cudaEvent_t ev[2] = {nullptr, nullptr}; LgbCuBinnedMatrix* m = nullptr;
@@ -150,7 +150,7 @@ int lgbcu_bin_matrix(int device, const void* data, int data_type, int32_t nrow, 
 
 int lgbcu_binned_copy_to_host(LgbCuBinnedMatrix* m, uint8_t* out) {
   NEED(m && out, "lgbcu_binned_copy_to_host: NULL argument");
-  CU(cudaSetDevice(m->device));
+  USE_DEVICE(m->device);
   CU(cudaMemcpy(out, m->d_bins, (size_t)m->nrow * m->nfeat, cudaMemcpyDeviceToHost));
   return 0;
 }
@@ -165,6 +165,7 @@ int lgbcu_binned_device(const LgbCuBinnedMatrix* m, int* device) {
 int lgbcu_set_dataset_binned(LgbCuContext* c, const LgbCuBinnedMatrix* m, const LgbCuFeatureMeta* meta) {
   NEED(c && m && meta, "lgbcu_set_dataset_binned: NULL argument");
   NEED(m->device == c->device, "lgbcu_set_dataset_binned: the matrix lives on device %d, the learner on device %d", m->device, c->device);
+  USE_DEVICE(c->device);
   if (setup_dataset_common(c, m->nrow, m->nfeat, meta)) return -1;
   LAUNCH(k_pad_rows, grid_for(c, (long long)m->nrow * (c->stride / 4), 256), 256, 0, c->stream, (long long)m->nrow,
          m->nfeat, c->stride, m->d_bins, c->d_bins);

@@ -44,6 +44,20 @@ int fail(const char* fmt, ...) {
     if (e__ != cudaSuccess) return fail("CUDA error %s at %s:%d (%s)", cudaGetErrorString(e__), __FILE__, __LINE__, #call); \
   } while (0)
 
+// Every entry point works on its context's device and leaves the caller's current device as it found it: the host
+// application (torch, for one) may be working on another GPU in the same thread.
+struct ScopedDevice {
+  int prev = -1; bool switched = false; cudaError_t err = cudaSuccess;
+  explicit ScopedDevice(int dev) {
+    err = cudaGetDevice(&prev);
+    if (err == cudaSuccess && prev != dev) { err = cudaSetDevice(dev); switched = err == cudaSuccess; }
+  }
+  ~ScopedDevice() { if (switched) cudaSetDevice(prev); }
+};
+#define USE_DEVICE(dev)                  \
+  ScopedDevice scoped_device__(dev);     \
+  if (scoped_device__.err != cudaSuccess) return fail("CUDA error %s selecting device %d at %s:%d", cudaGetErrorString(scoped_device__.err), (int)(dev), __FILE__, __LINE__)
+
 #define LAUNCH(kernel, grid, block, smem, stream, ...)                                             \
   do {                                                                                             \
     kernel<<<(grid), (block), (smem), (stream)>>>(__VA_ARGS__);                                    \
@@ -221,7 +235,7 @@ int ensure_tree_buffers(LgbCuContext* c) {
   if (c->alloc_leaves == L && c->alloc_lookahead == K && c->d_pool) return 0;
   c->lookahead = K;  // the memory guard below may lower it; alloc_lookahead remembers what was asked for
   drop_graph(c);
-  CU(cudaSetDevice(c->device));
+  USE_DEVICE(c->device);
   // histogram slots: the root + one fresh slot per (round, item); a round commits at least one leaf, so there are at
   // most L-1 rounds after the root.  Keep the pool under 1/8 of the device memory by lowering K if necessary.
   {
@@ -375,7 +389,7 @@ int lgbcu_create(int device_id, LgbCuContext** out) {
                 e != cudaSuccess ? cudaGetErrorString(e) : "device count is 0");
   }
   NEED(device_id >= 0 && device_id < n, "lgbcu_create: device %d out of range (have %d)", device_id, n);
-  CU(cudaSetDevice(device_id));
+  USE_DEVICE(device_id);
   LgbCuContext* c = new LgbCuContext();
   struct Guard { LgbCuContext* c; ~Guard() { if (c) lgbcu_destroy(c); } } guard{c};   // a failure below frees the half-built context
   c->device = device_id;
@@ -431,7 +445,7 @@ int lgbcu_create(int device_id, LgbCuContext** out) {
 
 int lgbcu_destroy(LgbCuContext* c) {
   if (!c) return 0;
-  cudaSetDevice(c->device);
+  ScopedDevice dev_(c->device);
   if (c->stream) cudaStreamSynchronize(c->stream);
   drop_graph(c);
   lgbcu_comm_destroy(c);
@@ -456,6 +470,7 @@ int lgbcu_destroy(LgbCuContext* c) {
 
 int lgbcu_synchronize(LgbCuContext* c) {
   NEED(c, "lgbcu: NULL context");
+  USE_DEVICE(c->device);
   CU(cudaStreamSynchronize(c->stream));
   return 0;
 }
@@ -464,7 +479,7 @@ static int setup_dataset_common(LgbCuContext* c, int32_t num_data, int32_t num_f
   NEED(c, "lgbcu: NULL context");
   NEED(num_data > 0 && num_features > 0 && meta, "lgbcu_set_dataset: empty dataset");
   NEED(num_features < (1 << KEY_FEAT_BITS), "lgbcu_set_dataset: %d features exceed the supported %d", num_features, (1 << KEY_FEAT_BITS) - 1);
-  CU(cudaSetDevice(c->device));
+  USE_DEVICE(c->device);
   c->N = num_data; c->F = num_features;
   c->stride = (num_features + 15) & ~15;
   c->ntiles16 = c->stride / 16;
@@ -517,7 +532,8 @@ static int setup_dataset_common(LgbCuContext* c, int32_t num_data, int32_t num_f
 
 int lgbcu_set_dataset(LgbCuContext* c, int32_t num_data, int32_t num_features, const uint8_t* bins,
                       const LgbCuFeatureMeta* meta) {
-  NEED(bins, "lgbcu_set_dataset: bins is NULL");
+  NEED(c && bins, "lgbcu_set_dataset: NULL argument");
+  USE_DEVICE(c->device);
   if (setup_dataset_common(c, num_data, num_features, meta)) return -1;
   {
     // one contiguous H2D copy, then pad rows to the 16-byte stride on the device (a strided 2-D copy of 28-byte rows
@@ -539,7 +555,8 @@ int lgbcu_set_dataset(LgbCuContext* c, int32_t num_data, int32_t num_features, c
 
 int lgbcu_set_dataset_columns(LgbCuContext* c, int32_t num_data, int32_t num_features, const uint8_t* const* columns,
                               const LgbCuFeatureMeta* meta) {
-  NEED(columns, "lgbcu_set_dataset_columns: columns is NULL");
+  NEED(c && columns, "lgbcu_set_dataset_columns: NULL argument");
+  USE_DEVICE(c->device);
   if (setup_dataset_common(c, num_data, num_features, meta)) return -1;
   CU(cudaMemsetAsync(c->d_bins, 0, (size_t)num_data * c->stride, c->stream));
   struct Tmp { uint8_t* p[2] = {nullptr, nullptr}; ~Tmp() { for (auto q : p) if (q) cudaFree(q); } } T;   // released on every way out
@@ -583,7 +600,7 @@ int lgbcu_set_hist_mode(LgbCuContext* c, int mode) {
 int lgbcu_set_label(LgbCuContext* c, const float* label, int32_t n) {
   NEED(c && label, "lgbcu_set_label: NULL argument");
   NEED(n == c->N, "lgbcu_set_label: length %d != num_data %d", n, c->N);
-  CU(cudaSetDevice(c->device));
+  USE_DEVICE(c->device);
   CU(dev_alloc(&c->d_label, (size_t)n));
   CU(cudaMemcpyAsync(c->d_label, label, sizeof(float) * n, cudaMemcpyHostToDevice, c->stream));
   CU(cudaStreamSynchronize(c->stream));
@@ -595,7 +612,7 @@ int lgbcu_set_weight(LgbCuContext* c, const float* weight, int32_t n) {
   NEED(c, "lgbcu: NULL context");
   if (!weight) { c->has_weight = false; return 0; }
   NEED(n == c->N, "lgbcu_set_weight: length %d != num_data %d", n, c->N);
-  CU(cudaSetDevice(c->device));
+  USE_DEVICE(c->device);
   CU(dev_alloc(&c->d_weight, (size_t)n));
   CU(cudaMemcpyAsync(c->d_weight, weight, sizeof(float) * n, cudaMemcpyHostToDevice, c->stream));
   CU(cudaStreamSynchronize(c->stream));
@@ -606,7 +623,7 @@ int lgbcu_set_weight(LgbCuContext* c, const float* weight, int32_t n) {
 int lgbcu_set_query(LgbCuContext* c, const int32_t* boundaries, int32_t num_queries) {
   NEED(c && boundaries && num_queries > 0, "lgbcu_set_query: bad argument");
   NEED(boundaries[0] == 0 && boundaries[num_queries] == c->N, "lgbcu_set_query: boundaries must span [0, num_data]");
-  CU(cudaSetDevice(c->device));
+  USE_DEVICE(c->device);
   c->h_query.assign(boundaries, boundaries + num_queries + 1);
   c->num_queries = num_queries;
   c->max_query = 0;
@@ -632,7 +649,7 @@ int lgbcu_set_objective(LgbCuContext* c, int kind, double p0, double p1, double 
 
 int lgbcu_set_label_gain(LgbCuContext* c, const double* label_gain, int32_t n) {
   NEED(c && label_gain && n > 0, "lgbcu_set_label_gain: bad argument");
-  CU(cudaSetDevice(c->device));
+  USE_DEVICE(c->device);
   CU(dev_alloc(&c->d_label_gain, (size_t)n));
   CU(cudaMemcpyAsync(c->d_label_gain, label_gain, sizeof(double) * n, cudaMemcpyHostToDevice, c->stream));
   CU(cudaStreamSynchronize(c->stream));
@@ -643,7 +660,7 @@ int lgbcu_set_label_gain(LgbCuContext* c, const double* label_gain, int32_t n) {
 int lgbcu_get_gradients(LgbCuContext* c) {
   NEED(c && c->N > 0, "lgbcu_get_gradients: dataset not set");
   NEED(c->has_label, "lgbcu_get_gradients: label not set");
-  CU(cudaSetDevice(c->device));
+  USE_DEVICE(c->device);
   const float* w = c->has_weight ? c->d_weight : nullptr;
   const int g = grid_for(c, c->N, 256);
   if (c->objective == LGBCU_OBJ_BINARY) {
@@ -663,7 +680,7 @@ int lgbcu_get_gradients(LgbCuContext* c) {
 int lgbcu_set_gradients(LgbCuContext* c, const float* grad, const float* hess, int32_t n) {
   NEED(c && grad && hess, "lgbcu_set_gradients: NULL argument");
   NEED(n == c->N, "lgbcu_set_gradients: length %d != num_data %d", n, c->N);
-  CU(cudaSetDevice(c->device));
+  USE_DEVICE(c->device);
   CU(cudaMemcpyAsync(c->d_grad, grad, sizeof(float) * n, cudaMemcpyHostToDevice, c->stream));
   CU(cudaMemcpyAsync(c->d_hess, hess, sizeof(float) * n, cudaMemcpyHostToDevice, c->stream));
   CU(cudaStreamSynchronize(c->stream));
@@ -672,7 +689,7 @@ int lgbcu_set_gradients(LgbCuContext* c, const float* grad, const float* hess, i
 
 int lgbcu_copy_gradients(LgbCuContext* c, float* grad, float* hess, int32_t n) {
   NEED(c && grad && hess && n == c->N, "lgbcu_copy_gradients: bad argument");
-  CU(cudaSetDevice(c->device));
+  USE_DEVICE(c->device);
   CU(cudaMemcpyAsync(grad, c->d_grad, sizeof(float) * n, cudaMemcpyDeviceToHost, c->stream));
   CU(cudaMemcpyAsync(hess, c->d_hess, sizeof(float) * n, cudaMemcpyDeviceToHost, c->stream));
   CU(cudaStreamSynchronize(c->stream));
@@ -681,7 +698,7 @@ int lgbcu_copy_gradients(LgbCuContext* c, float* grad, float* hess, int32_t n) {
 
 int lgbcu_set_score(LgbCuContext* c, const double* score, int32_t n) {
   NEED(c && c->N > 0, "lgbcu_set_score: dataset not set");
-  CU(cudaSetDevice(c->device));
+  USE_DEVICE(c->device);
   if (!score) { CU(cudaMemsetAsync(c->d_score, 0, sizeof(double) * c->N, c->stream)); return 0; }
   NEED(n == c->N, "lgbcu_set_score: length %d != num_data %d", n, c->N);
   CU(cudaMemcpyAsync(c->d_score, score, sizeof(double) * n, cudaMemcpyHostToDevice, c->stream));
@@ -691,7 +708,7 @@ int lgbcu_set_score(LgbCuContext* c, const double* score, int32_t n) {
 
 int lgbcu_add_score_const(LgbCuContext* c, double val) {
   NEED(c && c->N > 0, "lgbcu_add_score_const: dataset not set");
-  CU(cudaSetDevice(c->device));
+  USE_DEVICE(c->device);
   LAUNCH(k_add_const, grid_for(c, c->N, 256), 256, 0, c->stream, c->N, c->d_score, val);
   CU(cudaGetLastError());
   return 0;
@@ -699,7 +716,7 @@ int lgbcu_add_score_const(LgbCuContext* c, double val) {
 
 int lgbcu_copy_score(LgbCuContext* c, double* score, int32_t n) {
   NEED(c && score && n == c->N, "lgbcu_copy_score: bad argument");
-  CU(cudaSetDevice(c->device));
+  USE_DEVICE(c->device);
   // The caller's buffer is pageable (and usually untouched): stream the scores through two page-locked staging
   // buffers and let the host threads move each chunk on while the next one is in flight.
   const size_t CH = (size_t)1 << 19;  // doubles per chunk (4 MB)
@@ -762,7 +779,7 @@ int lgbcu_add_score_by_partition(LgbCuContext* c, const double* leaf_value, int3
   NEED(c && leaf_value, "lgbcu_add_score_by_partition: NULL argument");
   NEED(c->tree_begun, "lgbcu_add_score_by_partition: no tree has been grown");
   NEED(num_leaves >= 1 && num_leaves <= c->alloc_leaves, "lgbcu_add_score_by_partition: num_leaves %d out of range", num_leaves);
-  CU(cudaSetDevice(c->device));
+  USE_DEVICE(c->device);
   CU(cudaMemcpyAsync(c->d_leaf_value, leaf_value, sizeof(double) * num_leaves, cudaMemcpyHostToDevice, c->stream));
   const DevView V = c->view();
   // one block per 4096-position chunk; a leaf's last chunk may be partial, hence the num_leaves spare blocks
@@ -779,7 +796,7 @@ int lgbcu_add_score_by_tree(LgbCuContext* c, int32_t num_leaves, const int32_t* 
                             int64_t rows_tag) {
   NEED(c && c->N > 0, "lgbcu_add_score_by_tree: dataset not set");
   NEED(num_leaves >= 1 && leaf_value, "lgbcu_add_score_by_tree: bad tree");
-  CU(cudaSetDevice(c->device));
+  USE_DEVICE(c->device);
   const bool device_oob = rows == LGBCU_DEVICE_OOB;   // the out-of-bag tail of the bag lgbcu_bagging drew
   if (device_oob) { NEED(c->bag_ready, "lgbcu_add_score_by_tree: no bag has been drawn"); rows = nullptr; num_rows = c->N - c->bag_count; }
   const int n = (rows || device_oob) ? num_rows : c->N;
@@ -809,7 +826,7 @@ int lgbcu_add_score_by_tree(LgbCuContext* c, int32_t num_leaves, const int32_t* 
 
 int lgbcu_begin_tree(LgbCuContext* c, const int32_t* bag_indices, int32_t bag_count, const int8_t* feature_used) {
   NEED(c, "lgbcu: NULL context");
-  CU(cudaSetDevice(c->device));
+  USE_DEVICE(c->device);
   if (ensure_tree_buffers(c)) return -1;
   int identity = 1;
   if (bag_indices == LGBCU_DEVICE_BAG) {   // the bag lgbcu_bagging drew, already on the device
@@ -853,7 +870,7 @@ int lgbcu_num_total_bin(LgbCuContext* c, int32_t* out) {
 int lgbcu_hist_build(LgbCuContext* c, int32_t leaf) {
   NEED(c && c->tree_begun, "lgbcu_hist_build: call lgbcu_begin_tree first");
   NEED(leaf >= 0 && leaf < c->params.num_leaves, "lgbcu_hist_build: leaf %d out of range", leaf);
-  CU(cudaSetDevice(c->device));
+  USE_DEVICE(c->device);
   const DevView V = c->view();
   LAUNCH(k_zero_slot, grid_for(c, c->total_bin, 256), 256, 0, c->stream, V, leaf);
   cudaEvent_t e0 = nullptr, e1 = nullptr;
@@ -878,7 +895,7 @@ int lgbcu_hist_read(LgbCuContext* c, int32_t leaf, double* out, int64_t out_len)
   NEED(c && out && c->tree_begun, "lgbcu_hist_read: bad argument / no tree begun");
   NEED(out_len == 2LL * c->total_bin, "lgbcu_hist_read: out_len %lld != 2*total_bin %d", (long long)out_len, 2 * c->total_bin);
   NEED(leaf >= 0 && leaf < c->params.num_leaves, "lgbcu_hist_read: leaf %d out of range", leaf);
-  CU(cudaSetDevice(c->device));
+  USE_DEVICE(c->device);
   LAUNCH(k_hist_export, c->F, 256, 0, c->stream, c->view(), leaf, c->d_export);
   CU(cudaGetLastError());
   CU(cudaMemcpyAsync(out, c->d_export, sizeof(double) * 2 * c->total_bin, cudaMemcpyDeviceToHost, c->stream));
@@ -888,7 +905,7 @@ int lgbcu_hist_read(LgbCuContext* c, int32_t leaf, double* out, int64_t out_len)
 
 int lgbcu_hist_subtract(LgbCuContext* c, int32_t parent_leaf, int32_t smaller_leaf) {
   NEED(c && c->tree_begun, "lgbcu_hist_subtract: no tree begun");
-  CU(cudaSetDevice(c->device));
+  USE_DEVICE(c->device);
   LAUNCH(k_hist_subtract, grid_for(c, c->total_bin, 256), 256, 0, c->stream, c->view(), parent_leaf, smaller_leaf);
   CU(cudaGetLastError());
   return 0;
@@ -897,7 +914,7 @@ int lgbcu_hist_subtract(LgbCuContext* c, int32_t parent_leaf, int32_t smaller_le
 int lgbcu_find_best_split(LgbCuContext* c, int32_t leaf, LgbCuSplitInfo* out) {
   NEED(c && out && c->tree_begun, "lgbcu_find_best_split: bad argument / no tree begun");
   NEED(leaf >= 0 && leaf < c->params.num_leaves, "lgbcu_find_best_split: leaf %d out of range", leaf);
-  CU(cudaSetDevice(c->device));
+  USE_DEVICE(c->device);
   LAUNCH(k_find_split, dim3(c->F, 1), FS_THREADS, 0, c->stream, c->view(), 1, leaf);
   CU(cudaGetLastError());
   CU(cudaMemcpyAsync(c->h_split, c->d_best + leaf, sizeof(DevSplit), cudaMemcpyDeviceToHost, c->stream));
@@ -917,7 +934,7 @@ int lgbcu_partition(LgbCuContext* c, int32_t leaf, int32_t inner_feature, int32_
   NEED(leaf >= 0 && leaf < c->params.num_leaves && right_leaf > 0 && right_leaf < c->params.num_leaves && leaf != right_leaf,
        "lgbcu_partition: leaf ids out of range");
   NEED(inner_feature >= 0 && inner_feature < c->F, "lgbcu_partition: feature %d out of range", inner_feature);
-  CU(cudaSetDevice(c->device));
+  USE_DEVICE(c->device);
   const DevView V = c->view();
   LAUNCH(k_set_split, 1, 1, 0, c->stream, V, leaf, inner_feature, threshold, default_left, right_leaf);
   if (launch_partition(c, c->N, 1)) return -1;
@@ -931,7 +948,7 @@ int lgbcu_partition(LgbCuContext* c, int32_t leaf, int32_t inner_feature, int32_
 int lgbcu_leaf_indices(LgbCuContext* c, int32_t leaf, int32_t* out, int32_t capacity, int32_t* count) {
   NEED(c && count && c->tree_begun, "lgbcu_leaf_indices: bad argument / no tree begun");
   NEED(leaf >= 0 && leaf < c->params.num_leaves, "lgbcu_leaf_indices: leaf %d out of range", leaf);
-  CU(cudaSetDevice(c->device));
+  USE_DEVICE(c->device);
   CU(cudaMemcpyAsync(c->h_leaf, c->d_leaves + leaf, sizeof(DevLeaf), cudaMemcpyDeviceToHost, c->stream));
   CU(cudaStreamSynchronize(c->stream));
   const DevLeaf L = *c->h_leaf;
@@ -949,7 +966,7 @@ int lgbcu_leaf_indices(LgbCuContext* c, int32_t leaf, int32_t* out, int32_t capa
 int lgbcu_set_leaf_sums(LgbCuContext* c, int32_t leaf, double sum_g, double sum_h, double output) {
   NEED(c && c->tree_begun, "lgbcu_set_leaf_sums: no tree begun");
   NEED(leaf >= 0 && leaf < c->params.num_leaves, "lgbcu_set_leaf_sums: leaf %d out of range", leaf);
-  CU(cudaSetDevice(c->device));
+  USE_DEVICE(c->device);
   LAUNCH(k_set_leaf_sums, 1, 1, 0, c->stream, c->view(), leaf, sum_g, sum_h, output);
   CU(cudaGetLastError());
   return 0;
@@ -958,7 +975,7 @@ int lgbcu_set_leaf_sums(LgbCuContext* c, int32_t leaf, double sum_g, double sum_
 int lgbcu_get_leaf_sums(LgbCuContext* c, int32_t leaf, double* sum_g, double* sum_h, int32_t* count) {
   NEED(c && c->tree_begun, "lgbcu_get_leaf_sums: no tree begun");
   NEED(leaf >= 0 && leaf < c->params.num_leaves, "lgbcu_get_leaf_sums: leaf %d out of range", leaf);
-  CU(cudaSetDevice(c->device));
+  USE_DEVICE(c->device);
   CU(cudaMemcpyAsync(c->h_leaf, c->d_leaves + leaf, sizeof(DevLeaf), cudaMemcpyDeviceToHost, c->stream));
   CU(cudaStreamSynchronize(c->stream));
   if (sum_g) *sum_g = c->h_leaf->sum_g;
@@ -993,7 +1010,7 @@ static int enqueue_round(LgbCuContext* c, int round, cudaEvent_t* ev) {
 int lgbcu_train_tree(LgbCuContext* c, LgbCuSplitRecord* records, int32_t* num_splits) {
   NEED(c && records && num_splits, "lgbcu_train_tree: NULL argument");
   NEED(c->tree_begun, "lgbcu_train_tree: call lgbcu_begin_tree first");
-  CU(cudaSetDevice(c->device));
+  USE_DEVICE(c->device);
   const int L = c->params.num_leaves;
   const int K = c->lookahead;
   const bool prof = c->profile;
@@ -1102,7 +1119,7 @@ int lgbcu_train_tree(LgbCuContext* c, LgbCuSplitRecord* records, int32_t* num_sp
 
 int lgbcu_profile_phases(LgbCuContext* c, double* ms8) {
   NEED(c && ms8, "lgbcu_profile_phases: NULL argument");
-  CU(cudaSetDevice(c->device));
+  USE_DEVICE(c->device);
   CU(cudaMemcpyAsync(c->h_ctl, c->d_ctl, sizeof(DevCtl), cudaMemcpyDeviceToHost, c->stream));
   CU(cudaStreamSynchronize(c->stream));
   for (int i = 0; i < 8; ++i) ms8[i] = c->loop_phase_valid ? c->loop_phase_ms[i] : 0.0;
@@ -1145,7 +1162,7 @@ int lgbcu_profile_enable(LgbCuContext* c, int on) {
 
 int lgbcu_profile_read(LgbCuContext* c, double* hist_ms, int64_t* hist_calls, double* hist_bytes, int reset) {
   NEED(c, "lgbcu: NULL context");
-  CU(cudaSetDevice(c->device));
+  USE_DEVICE(c->device);
   CU(cudaMemcpyAsync(c->h_ctl, c->d_ctl, sizeof(DevCtl), cudaMemcpyDeviceToHost, c->stream));
   CU(cudaStreamSynchronize(c->stream));
   const unsigned long long rows = c->h_ctl->prof_hist_rows, rows_idx = c->h_ctl->prof_hist_rows_indexed;
@@ -1186,7 +1203,7 @@ int lgbcu_comm_init(LgbCuContext* c, const uint8_t* id128, int32_t rank, int32_t
   NEED(world_size >= 1 && rank >= 0 && rank < world_size, "lgbcu_comm_init: bad rank %d / world %d", rank, world_size);
   if (world_size == 1) { c->rank = 0; c->world = 1; return 0; }
   if (nccl_load()) return -1;
-  CU(cudaSetDevice(c->device));
+  USE_DEVICE(c->device);
   std::lock_guard<std::mutex> lock(g_comms_mu);
   for (const CachedComm& k : g_comms) {
     if (k.rank == rank && k.world == world_size && k.device == c->device && std::memcmp(k.id, id128, 128) == 0) {
@@ -1206,7 +1223,7 @@ int lgbcu_comm_init(LgbCuContext* c, const uint8_t* id128, int32_t rank, int32_t
 
 int lgbcu_comm_release_all(void) {
   std::lock_guard<std::mutex> lock(g_comms_mu);
-  for (const CachedComm& k : g_comms) { cudaSetDevice(k.device); g_nccl.CommDestroy(k.comm); }
+  for (const CachedComm& k : g_comms) { ScopedDevice dev_(k.device); g_nccl.CommDestroy(k.comm); }
   g_comms.clear();
   return 0;
 }
@@ -1214,7 +1231,7 @@ int lgbcu_comm_release_all(void) {
 int lgbcu_comm_allreduce_sum_f64(LgbCuContext* c, double* inout, int32_t n) {
   NEED(c && inout && n > 0 && n <= 64, "lgbcu_comm_allreduce_sum_f64: bad argument");
   if (!c->comm) return 0;
-  CU(cudaSetDevice(c->device));
+  USE_DEVICE(c->device);
   if (!c->d_scratch) CU(dev_alloc(&c->d_scratch, (size_t)64));
   CU(cudaMemcpyAsync(c->d_scratch, inout, sizeof(double) * n, cudaMemcpyHostToDevice, c->stream));
   NC(g_nccl.AllReduce(c->d_scratch, c->d_scratch, (size_t)n, ncclDouble, ncclSum, c->comm, c->stream));

@@ -47,7 +47,7 @@ int lgbcu_valid_create(LgbCuContext* c, int32_t num_data, const uint8_t* bins, i
   NEED(c && bins && out_set, "lgbcu_valid_create: NULL argument");
   NEED(c->N > 0, "lgbcu_valid_create: set the training data first");
   NEED(num_data > 0, "lgbcu_valid_create: empty validation set");
-  CU(cudaSetDevice(c->device));
+  USE_DEVICE(c->device);
   ValidSet v;
   v.n = num_data;
   CU(dev_alloc(&v.d_bins, (size_t)num_data * c->stride));
@@ -71,14 +71,14 @@ int lgbcu_valid_create(LgbCuContext* c, int32_t num_data, const uint8_t* bins, i
 int lgbcu_valid_set_label(LgbCuContext* c, int32_t set, const float* label, int32_t n) {
   ValidSet* v; if (valid_get(c, set, &v)) return -1;
   NEED(label && n == v->n, "lgbcu_valid_set_label: length %d != %d rows", n, v->n);
-  CU(cudaSetDevice(c->device));
+  USE_DEVICE(c->device);
   return upload_vec(c, &v->d_label, label, (size_t)n);
 }
 
 int lgbcu_valid_set_weight(LgbCuContext* c, int32_t set, const float* weight, int32_t n) {
   ValidSet* v; if (valid_get(c, set, &v)) return -1;
   NEED(weight && n == v->n, "lgbcu_valid_set_weight: length %d != %d rows", n, v->n);
-  CU(cudaSetDevice(c->device));
+  USE_DEVICE(c->device);
   return upload_vec(c, &v->d_weight, weight, (size_t)n);
 }
 
@@ -87,7 +87,7 @@ int lgbcu_valid_set_query(LgbCuContext* c, int32_t set, const int32_t* boundarie
   NEED(boundaries && num_queries > 0, "lgbcu_valid_set_query: bad argument");
   NEED(boundaries[0] == 0 && boundaries[num_queries] == v->n, "lgbcu_valid_set_query: boundaries must span [0, num_data]");
   for (int q = 0; q < num_queries; ++q) NEED(boundaries[q + 1] >= boundaries[q], "lgbcu_valid_set_query: boundaries not monotone");
-  CU(cudaSetDevice(c->device));
+  USE_DEVICE(c->device);
   v->num_queries = num_queries;
   return upload_vec(c, &v->d_query, boundaries, (size_t)num_queries + 1);
 }
@@ -95,7 +95,7 @@ int lgbcu_valid_set_query(LgbCuContext* c, int32_t set, const int32_t* boundarie
 int lgbcu_valid_set_score(LgbCuContext* c, int32_t set, const double* score, int32_t n) {
   ValidSet* v; if (valid_get(c, set, &v)) return -1;
   NEED(score && n == v->n, "lgbcu_valid_set_score: length %d != %d rows", n, v->n);
-  CU(cudaSetDevice(c->device));
+  USE_DEVICE(c->device);
   CU(cudaMemcpyAsync(v->d_score, score, sizeof(double) * n, cudaMemcpyHostToDevice, c->stream));
   CU(cudaStreamSynchronize(c->stream));
   return 0;
@@ -104,7 +104,7 @@ int lgbcu_valid_set_score(LgbCuContext* c, int32_t set, const double* score, int
 int lgbcu_valid_copy_score(LgbCuContext* c, int32_t set, double* out, int32_t n) {
   ValidSet* v; if (valid_get(c, set, &v)) return -1;
   NEED(out && n == v->n, "lgbcu_valid_copy_score: length %d != %d rows", n, v->n);
-  CU(cudaSetDevice(c->device));
+  USE_DEVICE(c->device);
   CU(cudaMemcpyAsync(out, v->d_score, sizeof(double) * n, cudaMemcpyDeviceToHost, c->stream));
   CU(cudaStreamSynchronize(c->stream));
   return 0;
@@ -112,7 +112,7 @@ int lgbcu_valid_copy_score(LgbCuContext* c, int32_t set, double* out, int32_t n)
 
 int lgbcu_valid_add_const(LgbCuContext* c, int32_t set, double value) {
   ValidSet* v; if (valid_get(c, set, &v)) return -1;
-  CU(cudaSetDevice(c->device));
+  USE_DEVICE(c->device);
   LAUNCH(k_add_const, grid_for(c, v->n, 256), 256, 0, c->stream, v->n, v->d_score, value);
   CU(cudaGetLastError());
   return 0;
@@ -123,7 +123,7 @@ int lgbcu_valid_add_tree(LgbCuContext* c, int32_t set, int32_t num_leaves, const
                          const int32_t* right_child, const double* leaf_value) {
   ValidSet* v; if (valid_get(c, set, &v)) return -1;
   NEED(num_leaves >= 1 && leaf_value, "lgbcu_valid_add_tree: bad tree");
-  CU(cudaSetDevice(c->device));
+  USE_DEVICE(c->device);
   if (num_leaves == 1) {  // constant tree (tree.cpp:110-118)
     if (leaf_value[0] == 0.0) return 0;
     return lgbcu_valid_add_const(c, set, leaf_value[0]);
@@ -150,7 +150,7 @@ int lgbcu_eval_set_ndcg(LgbCuContext* c, int32_t set, const int32_t* eval_at, in
   int max_k = 0;
   for (int i = 0; i < num_eval; ++i) { NEED(eval_at[i] > 0, "lgbcu_eval_set_ndcg: eval_at must be positive"); max_k = std::max(max_k, eval_at[i]); }
   NEED(max_k <= NDCG_MAX_K && max_k <= num_discount, "lgbcu_eval_set_ndcg: eval_at %d exceeds the supported %d", max_k, NDCG_MAX_K);
-  CU(cudaSetDevice(c->device));
+  USE_DEVICE(c->device);
   free_ndcg(t);
   if (upload_vec(c, &t->d_eval_at, eval_at, (size_t)num_eval)) return -1;
   if (upload_vec(c, &t->d_inv_max_dcg, inv_max_dcg, (size_t)nq * num_eval)) return -1;
@@ -238,7 +238,7 @@ int eval_auc(LgbCuContext* c, int n, const double* score, const float* label, co
 int lgbcu_eval(LgbCuContext* c, int32_t set, int32_t kind, double sigmoid, double* out, int32_t out_len) {
   NEED(c && out && out_len >= 1, "lgbcu_eval: bad argument");
   NEED(kind >= LGBCU_METRIC_L2 && kind <= LGBCU_METRIC_NDCG, "lgbcu_eval: unknown metric kind %d", kind);
-  CU(cudaSetDevice(c->device));
+  USE_DEVICE(c->device);
   int n; const double* score; const float* label; const float* weight; const int* query; int nq; NdcgTables* nd;
   if (set < 0) {
     NEED(c->N > 0, "lgbcu_eval: no training data");

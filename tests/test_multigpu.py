@@ -122,3 +122,29 @@ def test_row_shards_share_mappers_gloo_world2():
         p.join(timeout=180)
         assert p.exitcode == 0
     assert q.get(timeout=5) is True
+
+
+@pytest.mark.gpu
+def test_entry_points_leave_the_callers_current_device_alone():
+    """A host application may be working on another GPU in the same thread (torch does): dataset creation (device
+    binning), booster creation and training select their own device and put the caller's back."""
+    if N.device_count() < 2:
+        pytest.skip("needs 2 GPUs")
+    import torch
+    torch.cuda.set_device(1)
+    rng = np.random.default_rng(0)
+    X = rng.standard_normal((20_000, 6)).astype(np.float32)
+    y = (X[:, 0] + 0.3 * rng.standard_normal(20_000) > 0).astype(np.float32)
+    ours = capi.ours()
+    params = "objective=binary num_leaves=15 verbosity=-1 gpu_device_id=0"
+    ds = ours.dataset_from_mat(X, params)
+    assert torch.cuda.current_device() == 1
+    ours.set_field(ds, "label", y)
+    b = ours.booster_create(ds, params)
+    assert torch.cuda.current_device() == 1
+    for _ in range(3):
+        ours.update(b)
+    ours.get_predict(b, len(y))
+    assert torch.cuda.current_device() == 1
+    ours.booster_free(b); ours.dataset_free(ds)
+    assert torch.cuda.current_device() == 1

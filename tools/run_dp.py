@@ -28,7 +28,7 @@ if world > 1:
     torch.cuda.set_device(local)
     dist.init_process_group("nccl")
     lo, hi = rank * n // world, (rank + 1) * n // world
-    ds = ours.dataset_from_mat(np.ascontiguousarray(X[lo:hi]), base, reference=ref_ds)
+    ds = ours.dataset_from_mat(np.ascontiguousarray(X[lo:hi]), base + f" gpu_device_id={local}", reference=ref_ds)
     ours.set_field(ds, "label", np.ascontiguousarray(y[lo:hi]))
     uid = np.zeros(128, dtype=np.uint8)
     if rank == 0:
