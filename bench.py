@@ -442,7 +442,20 @@ def run_ours(args):
                "sample": f"same {n}x{N_FEAT} matrix and parameters, {k} iterations after 1 warm-up, force_col_wise, all host threads"}
         text_ref = ref.model_string(rb)
         pred_ref = ref.get_predict(rb, n)
-        ref.booster_free(rb); ref.dataset_free(rds)
+        ref.booster_free(rb)
+        # the reference's other histogram layout (row-wise multi-value bins), same dataset, same threads
+        try:
+            rw = ref.booster_create(rds, PARAMS + f" force_row_wise=true num_threads={cores}")
+            ref.update(rw)
+            t0 = time.perf_counter()
+            for _ in range(4):
+                ref.update(rw)
+            cpu["row_wise_value"] = 4 / (time.perf_counter() - t0)
+            cpu["row_wise_sample"] = "4 iterations after 1 warm-up, force_row_wise"
+            ref.booster_free(rw)
+        except Exception as ex:
+            cpu["row_wise_value"] = None; cpu["row_wise_sample"] = str(ex)[:200]
+        ref.dataset_free(rds)
         b = ours.booster_create(ds, params)
         for _ in range(PARITY_ITERS):
             ours.update(b)
