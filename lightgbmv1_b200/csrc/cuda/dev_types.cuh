@@ -111,6 +111,10 @@ struct DevCtl {
   DevFeat item_feat[LGB_KMAX];
 };
 
+// Feature ownership (data-parallel, wide data): what a rank sends to the all-gather per (leaf being expanded, child):
+// the best split over ITS features, with the key that SplitInfo::operator> compares.
+struct __align__(16) CandRec { DevSplit split; SplitKey key; };
+
 struct DevParams {   // LgbCuTreeParams + derived switches
   int num_leaves, max_depth, min_data_in_leaf;
   int use_l1, use_max_output, use_smoothing;
@@ -121,6 +125,10 @@ struct DevParams {   // LgbCuTreeParams + derived switches
 struct DevView {
   int num_data, num_features, row_stride, total_bin, num_tiles16;
   int data_parallel;         // 1: histograms are all-reduced across ranks, leaf counts are the global estimates
+  int f_begin, f_end;        // features this rank scans in k_find_split: all of them, or its block in ownership mode
+  int comm_size;             // ranks (ownership mode: rows of cand_all per (leaf, child))
+  CandRec* cand_send;        // [2 * LGB_KMAX]              ownership mode: this rank's winners of the round
+  CandRec* cand_all;         // [comm_size][2 * LGB_KMAX]   every rank's, after the all-gather
   const uint8_t* bins;
   const uint8_t* bins_col;   // column-major copy [F][col_stride]: the partition reads ONE feature of a leaf's rows -- a
   long long col_stride;      // sector of this copy holds that feature of 32 neighbouring rows, a sector of `bins` of one

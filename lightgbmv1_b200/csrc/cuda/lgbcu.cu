@@ -113,6 +113,10 @@ struct LgbCuContext {
   double* d_ndcg_per_query = nullptr; size_t ndcg_cap = 0;
   // data-parallel
   ncclComm_t comm = nullptr; int rank = 0, world = 1;
+  // feature ownership (comm.cuh): on for wide data, LGBCU_DP_OWNERSHIP forces it
+  bool dp_owner = false; int dp_owner_cfg = -1;
+  std::vector<int> own_begin;   // [world + 1] first feature of every rank's block
+  CandRec* d_cand_send = nullptr; CandRec* d_cand_all = nullptr;
   int num_sms = 148;
   cudaStream_t stream = nullptr;
   // dataset
@@ -194,6 +198,8 @@ struct LgbCuContext {
     V.pool = d_pool; V.leaves = d_leaves; V.best = d_best; V.feat_best = d_feat_best; V.feat_key = d_feat_key; V.leaf_key = d_leaf_key; V.ctl = d_ctl;
     V.records = d_records; V.part_sync = d_part_sync; V.bins_col = d_bins_col; V.col_stride = col_stride; V.part_bits = d_part_bits; V.p = params;
     V.data_parallel = (comm != nullptr || force_dp_counts) ? 1 : 0;
+    V.f_begin = 0; V.f_end = F; V.comm_size = world; V.cand_send = d_cand_send; V.cand_all = d_cand_all;
+    if (dp_owner && (int)own_begin.size() == world + 1) { V.f_begin = own_begin[rank]; V.f_end = own_begin[rank + 1]; }
     return V;
   }
 };
@@ -310,10 +316,70 @@ int comm_allreduce_tree_setup(LgbCuContext* c) {
 
 // Split s builds the smaller leaf's histogram in pool slot s (slot 0 = root, then the fresh slot of split s
 // is s): known on the host without reading device state, so the collective can be enqueued blind.
-int comm_reduce_hist(LgbCuContext* c, int first_slot, int num_slots) {
+int comm_reduce_hist(LgbCuContext* c, int first_slot, int num_slots, bool root_round) {
   if (!c->comm) return 0;
   HistEntry* slot = c->d_pool + (size_t)first_slot * c->total_bin;
-  NC(g_nccl.AllReduce(slot, slot, (size_t)c->total_bin * 2 * num_slots, ncclInt64, ncclSum, c->comm, c->stream));
+  if (!c->dp_owner) {
+    NC(g_nccl.AllReduce(slot, slot, (size_t)c->total_bin * 2 * num_slots, ncclInt64, ncclSum, c->comm, c->stream));
+    return 0;
+  }
+  // Ownership mode (comm.cuh): every owner receives the global sums of its feature block, for each fresh slot.  The
+  // root's feature 0 goes to every rank first: LeafSplits::Init's root sums are read off it (k_root_sums).
+  int skip0 = 0;
+  if (root_round) {
+    const DevFeat& f0 = c->h_feats[0];
+    HistEntry* b0 = slot + f0.hist_base;
+    NC(g_nccl.AllReduce(b0, b0, (size_t)f0.nslots * 2, ncclInt64, ncclSum, c->comm, c->stream));
+    skip0 = 1;
+  }
+  NC(g_nccl.GroupStart());
+  for (int k = 0; k < num_slots; ++k) {
+    for (int r = 0; r < c->world; ++r) {
+      int fb = c->own_begin[r], fe = c->own_begin[r + 1];
+      if (skip0 && fb == 0) fb = 1;   // already global everywhere
+      if (fb >= fe) continue;
+      const size_t e0 = (size_t)c->h_feats[fb].hist_base;
+      const size_t e1 = fe < c->F ? (size_t)c->h_feats[fe].hist_base : (size_t)c->total_bin;
+      HistEntry* blk = slot + (size_t)k * c->total_bin + e0;
+      NC(g_nccl.Reduce(blk, blk, (e1 - e0) * 2, ncclInt64, ncclSum, r, c->comm, c->stream));
+    }
+  }
+  NC(g_nccl.GroupEnd());
+  return 0;
+}
+
+// ownership mode: every rank's per-(leaf, child) winners to every rank
+int comm_gather_winners(LgbCuContext* c) {
+  NC(g_nccl.AllGather(c->d_cand_send, c->d_cand_all, sizeof(CandRec) * 2 * LGB_KMAX, ncclChar, c->comm, c->stream));
+  return 0;
+}
+
+// Decided once the communicator and the data shape are known: ownership pays when the replicated split search is what
+// a round waits for (wide data); for narrow data the search costs no wall time and the extra collective would.
+int setup_ownership(LgbCuContext* c) {
+  bool want = c->comm != nullptr && c->world > 1 && c->F >= 256;
+  if (c->dp_owner_cfg == 0) want = false;
+  if (c->dp_owner_cfg == 1) want = c->comm != nullptr && c->world > 1;
+  if (want && !g_nccl.has_ownership_calls()) want = false;
+  if (want && c->F < c->world) want = false;
+  if (want == c->dp_owner && (!want || (int)c->own_begin.size() == c->world + 1)) return 0;
+  drop_graph(c);
+  c->dp_owner = want;
+  if (!want) return 0;
+  // contiguous feature blocks balanced by histogram entries; identical on every rank (same mappers)
+  c->own_begin.assign((size_t)c->world + 1, c->F);
+  c->own_begin[0] = 0;
+  int f = 0;
+  for (int r = 0; r < c->world; ++r) {
+    c->own_begin[r] = f;
+    const long long target = (long long)c->total_bin * (r + 1) / c->world;
+    const int must_leave = c->world - 1 - r;   // at least one feature for every later rank
+    while (f < c->F - must_leave && (f == c->own_begin[r] || (long long)c->h_feats[f].hist_base + c->h_feats[f].nslots <= target)) ++f;
+  }
+  c->own_begin[c->world] = c->F;
+  if (!c->d_cand_send) CU(dev_alloc(&c->d_cand_send, (size_t)2 * LGB_KMAX));
+  if (c->d_cand_all) { cudaFree(c->d_cand_all); c->d_cand_all = nullptr; }
+  CU(dev_alloc(&c->d_cand_all, (size_t)c->world * 2 * LGB_KMAX));
   return 0;
 }
 
@@ -397,6 +463,7 @@ int lgbcu_create(int device_id, LgbCuContext** out) {
   CU(cudaGetDeviceProperties(&prop, device_id));
   c->num_sms = prop.multiProcessorCount;
   if (const char* e = std::getenv("LGBCU_HIST_MIN_ROWS")) { const int v = std::atoi(e); if (v >= 1) c->hist_min_rows = v; }
+  if (const char* e = std::getenv("LGBCU_DP_OWNERSHIP")) c->dp_owner_cfg = std::atoi(e) != 0 ? 1 : 0;
   if (const char* e = std::getenv("LGBCU_HIST_SMALL_ROWS")) { const int v = std::atoi(e); if (v >= 0) c->hist_small_rows = v; }
   CU(cudaStreamCreateWithFlags(&c->stream, cudaStreamNonBlocking));
   CU(dev_alloc(&c->d_ctl, 1));
@@ -455,7 +522,8 @@ int lgbcu_destroy(LgbCuContext* c) {
                   c->d_inv_max_dcg, c->d_sigmoid_table, c->d_pool, c->d_splittable, c->d_leaves, c->d_best,
                   c->d_feat_best, c->d_ctl, c->d_records, c->d_leaf_value, c->d_export, c->d_tree_i32, c->d_tree_i8,
                   c->d_tree_f64, c->d_rows, c->d_scratch, c->d_parent_split, c->d_mfb_fix, c->d_feat_key, c->d_leaf_key, c->d_spec, c->d_expanded,
-                  c->d_bag_state, c->d_bag_bits, c->d_bag_tile, c->d_bag_ctl, c->d_bag, c->d_goss, c->d_goss_amp, c->d_goss_mult};
+                  c->d_bag_state, c->d_bag_bits, c->d_bag_tile, c->d_bag_ctl, c->d_bag, c->d_goss, c->d_goss_amp, c->d_goss_mult,
+                  c->d_cand_send, c->d_cand_all};
   for (void* p : ptrs) if (p) cudaFree(p);
   if (c->h_records) cudaFreeHost(c->h_records);
   if (c->h_ctl) cudaFreeHost(c->h_ctl);
@@ -828,6 +896,7 @@ int lgbcu_begin_tree(LgbCuContext* c, const int32_t* bag_indices, int32_t bag_co
   NEED(c, "lgbcu: NULL context");
   USE_DEVICE(c->device);
   if (ensure_tree_buffers(c)) return -1;
+  if (setup_ownership(c)) return -1;
   int identity = 1;
   if (bag_indices == LGBCU_DEVICE_BAG) {   // the bag lgbcu_bagging drew, already on the device
     NEED(c->bag_ready, "lgbcu_begin_tree: no bag has been drawn (lgbcu_bagging)");
@@ -996,10 +1065,16 @@ static int enqueue_round(LgbCuContext* c, int round, cudaEvent_t* ev) {
   if (c->comm) {  // slots of a round are a function of (round, item): the collective is enqueued blind
     const int first = round == 0 ? 0 : 1 + (round - 1) * K, count = round == 0 ? 1 : K;
     NEED(first + count <= c->pool_slots, "lgbcu_train_tree: round %d needs histogram slots [%d, %d) but the pool has %d", round, first, first + count, c->pool_slots);
-    if (comm_reduce_hist(c, first, count)) return -1;
+    if (comm_reduce_hist(c, first, count, round == 0)) return -1;
   }
   if (round == 0) LAUNCH(k_root_sums, 1, 32, 0, c->stream, V);
   if (ev) CU(cudaEventRecord(ev[1], c->stream));
+  if (c->comm && c->dp_owner) {
+    // owned scan -> all-gather of the winners -> control step
+    LAUNCH(k_find_split, dim3(V.f_end - V.f_begin, 2 * K), FS_THREADS, 0, c->stream, V, FS_MODE_OWNED, -1);
+    if (comm_gather_winners(c)) return -1;
+    LAUNCH(k_find_split, dim3(1, 1), FS_THREADS, 0, c->stream, V, FS_MODE_CONTROL, -1);
+  } else
   LAUNCH(k_find_split, dim3(c->F, 2 * K), FS_THREADS, 0, c->stream, V, 0, -1);
   if (ev) CU(cudaEventRecord(ev[2], c->stream));
   if (launch_partition(c, c->root_count, 0)) return -1;

@@ -221,6 +221,8 @@ __device__ __forceinline__ int key_pack(int feature, int threshold, int default_
 }
 
 #define FS_THREADS 256
+#define FS_MODE_OWNED 2     /* k_find_split modes beside 0 (training) and 1 (one explicit leaf): owned scan -> send buffer */
+#define FS_MODE_CONTROL 3   /* ... and the control step alone, from the gathered winners */
 #define FS_WARPS (FS_THREADS / 32)
 
 // Shared-memory work area of one (feature, leaf) block.
@@ -946,12 +948,14 @@ __global__ void __launch_bounds__(FS_THREADS, 4) k_find_split(DevView V, int mod
   __shared__ ScanSmem S;
   __shared__ int s_last;
   DevCtl* c = V.ctl;
-  if (mode == 0 && c->done) return;
+  if (mode != 1 && c->done) return;
   STAGE_BEGIN();
   STAMP(c, 1);
-  const int f = blockIdx.x, y = blockIdx.y, e = y >> 1, sel = y & 1;
-  const bool root_round = mode == 0 && c->round == 0;
-  const int ni = mode == 0 ? (root_round ? 1 : c->num_items) : 1;
+  // training launches scan this rank's features only: all of them, or its block in ownership mode (comm.cuh)
+  const int f = (mode == 1 ? 0 : V.f_begin) + blockIdx.x, f_end = mode == 1 ? V.num_features : V.f_end;
+  const int y = blockIdx.y, e = y >> 1, sel = y & 1;
+  const bool root_round = mode != 1 && c->round == 0;
+  const int ni = mode != 1 ? (root_round ? 1 : c->num_items) : 1;
   FindTarget T;
   bool active = false;
   if (mode == 1 || root_round) {
@@ -974,17 +978,19 @@ __global__ void __launch_bounds__(FS_THREADS, 4) k_find_split(DevView V, int mod
     }
   }
   STAGE(0);
-  if (active) find_item(V, S, f, sel, T);
-  STAGE(4);
-  __threadfence();
-  __syncthreads();
-  if (threadIdx.x == 0) {
-    const unsigned ticket = atomicAdd(&c->feat_done, 1u);
-    s_last = (ticket == gridDim.x * gridDim.y - 1);
+  if (mode != FS_MODE_CONTROL) {
+    if (active && f < f_end) find_item(V, S, f, sel, T);
+    STAGE(4);
+    __threadfence();
+    __syncthreads();
+    if (threadIdx.x == 0) {
+      const unsigned ticket = atomicAdd(&c->feat_done, 1u);
+      s_last = (ticket == gridDim.x * gridDim.y - 1);
+    }
+    __syncthreads();
+    STAGE(5);
+    if (!s_last) return;
   }
-  __syncthreads();
-  STAGE(5);
-  if (!s_last) return;
   // ---- control step, last block only.  Step 1: every warp reduces feat_key rows (one leaf each) and stores that
   // leaf's best split where it belongs.
   __shared__ CtrlShared C;
@@ -996,8 +1002,51 @@ __global__ void __launch_bounds__(FS_THREADS, 4) k_find_split(DevView V, int mod
 #else
 #define QSTAGE(i) do {} while (0)
 #endif
-  if (threadIdx.x == 0) c->feat_done = 0;
-  if (mode == 1 || root_round) {
+  if (threadIdx.x == 0 && mode != FS_MODE_CONTROL) c->feat_done = 0;
+  if (mode == FS_MODE_OWNED) {
+    // Ownership mode, first half: this rank's winners over ITS features go to the send buffer of the all-gather; the
+    // control step runs in a second launch (FS_MODE_CONTROL) once every rank's winners have arrived.
+    const int rows = root_round ? 1 : 2 * ni;
+    for (int p = warp; p < rows; p += FS_WARPS) {
+      bool live;
+      if (root_round) live = !c->skip_find;
+      else live = !V.spec[c->item_leaf[p >> 1]].skip_find;
+      CandRec* dst = &V.cand_send[p];
+      if (live) {
+        const PairBest b = warp_reduce_feature_keys(V, p, lane, V.f_begin, V.f_end);
+        store_leaf_best(V, p, b, &dst->split, &dst->key, lane);
+      } else {
+        store_none_split(&dst->split, lane);
+        if (lane == 0) store_key(&dst->key, none_key());
+      }
+    }
+    return;
+  }
+  if (mode == FS_MODE_CONTROL) {
+    // Ownership mode, second half (one block): per (leaf, child) row the best of the ranks' winners -- the same
+    // SplitInfo::operator> order, and the ranks' features are disjoint, so the winner is the one a scan of all
+    // features would have found (SyncUpGlobalBestSplit, parallel_tree_learner.h:190-213).
+    const int rows = root_round ? 1 : 2 * ni;
+    for (int p = warp; p < rows; p += FS_WARPS) {
+      DevSplit* dsplit; SplitKey* dkey;
+      if (root_round) {
+        if (c->skip_find) continue;
+        dsplit = &V.best[0]; dkey = &V.leaf_key[0];
+      } else {
+        DevSpec* sp = &V.spec[c->item_leaf[p >> 1]];
+        const int child = (p & 1) == 0 ? sp->smaller : 1 - sp->smaller;
+        dsplit = &sp->best[child]; dkey = &sp->key[child];
+      }
+      SplitKey k = none_key();
+      if (lane < V.comm_size) k = load_key_cg(&V.cand_all[(size_t)lane * (2 * LGB_KMAX) + p].key);
+      const unsigned tie = k.real_feature == -1 ? 0x7fffffffu : (unsigned)k.real_feature;
+      int w = warp_argmax(k.gain, tie, (unsigned)lane, lane < V.comm_size && k.gain == k.gain);
+      if (w < 0) w = 0;  // only NaN gains: rank 0's record
+      const CandRec* src = &V.cand_all[(size_t)w * (2 * LGB_KMAX) + p];
+      warp_copy_words(dsplit, &src->split, DEVSPLIT_WORDS, lane);
+      if (lane == 0) store_key(dkey, load_key_cg(&src->key));
+    }
+  } else if (mode == 1 || root_round) {
     const int leaf = mode == 1 ? leaf_arg : 0;
     if (warp == 0 && (mode == 1 || !c->skip_find)) {
       const PairBest b = warp_reduce_feature_keys(V, 0, lane);

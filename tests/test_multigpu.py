@@ -26,14 +26,14 @@ GOLDEN = os.path.join(H.ROOT, "tests", "golden", "dp_reference_2rank_model.txt")
 SCRIPT = os.path.join(H.ROOT, "tools", "run_dp.py")
 
 
-def _torchrun(nproc, port, out, extra="", sorted_shards=False):
+def _torchrun(nproc, port, out, extra="", sorted_shards=False, env=None):
     cmd = [sys.executable, "-m", "torch.distributed.run", "--nnodes=1", f"--nproc-per-node={nproc}",
            "--master-addr", "127.0.0.1", "--master-port", str(port), SCRIPT, "--out", out]
     if extra:
         cmd += ["--extra", extra]
     if sorted_shards:
         cmd += ["--sorted-shards"]
-    subprocess.check_call(cmd, env=dict(os.environ), timeout=900)
+    subprocess.check_call(cmd, env=dict(os.environ, **(env or {})), timeout=900)
 
 
 def _assert_same(a, b, what):
@@ -60,6 +60,26 @@ def test_two_rank_model_equals_reference_two_machine_model_and_one_rank_model(tm
     same, n, first = capi.compare_models(a, b, rtol_value=0.0)
     assert same == n, (same, n, first)
     assert a.split("parameters:")[0] == b.split("parameters:")[0]
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("sorted_shards", [False, True])
+def test_two_rank_feature_ownership_mode(tmp_path, sorted_shards):
+    """The reference's own scheme (data_parallel_tree_learner.cpp:176-247): every rank owns a block of features, gets
+    the global histogram of that block only (grouped ncclReduce), scans it, and the per-leaf winners are all-gathered
+    and reduced with SplitInfo::operator> on every rank.  Chosen by shape for wide data; forced here.  Same model as
+    the all-reduce mode, i.e. the reference's 2-machine model and the 1-rank model."""
+    if N.device_count() < 2:
+        pytest.skip("needs 2 GPUs")
+    one, two = str(tmp_path / "one.txt"), str(tmp_path / "two.txt")
+    cmd = [sys.executable, SCRIPT, "--out", one] + (["--sorted-shards"] if sorted_shards else [])
+    subprocess.check_call(cmd, env=dict(os.environ, LGBCU_FORCE_DP_COUNTS="1"), timeout=600)
+    _torchrun(2, 29513 + int(sorted_shards), two, sorted_shards=sorted_shards, env={"LGBCU_DP_OWNERSHIP": "1"})
+    a, b = open(one).read(), open(two).read()
+    if not sorted_shards:
+        _assert_same(open(GOLDEN).read(), b, "reference 2-machine socket run vs 2-rank NCCL run with feature ownership")
+    same, n, first = capi.compare_models(a, b, rtol_value=0.0)
+    assert same == n, (same, n, first)
 
 
 @pytest.mark.gpu
