@@ -136,18 +136,26 @@ def run_reference(args):
     n = args.rows
     X, y = higgs_shaped(n)
     ref = capi.reference()
-    params = PARAMS + f" force_col_wise=true num_threads={cores}"
-    ds = ref.dataset_from_mat(X, params)
-    ref.set_field(ds, "label", y)
-    b = ref.booster_create(ds, params)
-    for _ in range(args.warmup):
-        ref.update(b)
-    t0 = time.perf_counter()
-    for _ in range(args.steps):
-        ref.update(b)
-    dt = time.perf_counter() - t0
-    v = args.steps / dt
-    ref.booster_free(b); ref.dataset_free(ds)
+    # The reference has two histogram layouts on the CPU (column-wise DenseBin scans / row-wise multi-value bins) and
+    # picks one by timing both on the first iteration; both are timed here explicitly and the FASTER one is the arm's
+    # value -- on 16 cores and this shape that is row-wise.
+    per_mode = {}
+    for mode in ("row", "col"):
+        params = PARAMS + f" force_{mode}_wise=true num_threads={cores}"
+        ds = ref.dataset_from_mat(X, params)
+        ref.set_field(ds, "label", y)
+        b = ref.booster_create(ds, params)
+        for _ in range(args.warmup):
+            ref.update(b)
+        t0 = time.perf_counter()
+        for _ in range(args.steps):
+            ref.update(b)
+        per_mode[mode] = args.steps / (time.perf_counter() - t0)
+        ref.booster_free(b); ref.dataset_free(ds)
+    best = max(per_mode, key=per_mode.get)
+    v = per_mode[best]
+    dt = args.steps / v
+    params = PARAMS + f" force_{best}_wise=true num_threads={cores}"
     # e2e: the same K iterations from the host matrix (LGBM_DatasetCreateFromMat .. LGBM_BoosterGetPredict), / K
     t0 = time.perf_counter()
     ds = ref.dataset_from_mat(X, params)
@@ -163,7 +171,8 @@ def run_reference(args):
         "scaling": "strong", "vs_baseline": None, "dtype": "f64", "data": "synthetic",
         "config": config_of(n),
         "cpu_baseline": {"value": v, "unit": "iters/s", "cores": cores, "kind": "reference",
-                         "sample": f"full workload, {args.steps} iterations after {args.warmup} warm-up, force_col_wise"},
+                         "sample": f"full workload, {args.steps} iterations after {args.warmup} warm-up, force_{best}_wise (the faster of the reference's two layouts)",
+                         "col_wise_value": per_mode["col"], "row_wise_value": per_mode["row"]},
         # the contract wants the line's own value here (no copies on the host arm); the same from-the-matrix pipeline the
         # other arm's e2e times is reported beside it
         "e2e": {"value": v, "unit": "iters/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0,
@@ -452,6 +461,12 @@ def run_ours(args):
                 ref.update(rw)
             cpu["row_wise_value"] = 4 / (time.perf_counter() - t0)
             cpu["row_wise_sample"] = "4 iterations after 1 warm-up, force_row_wise"
+            cpu["col_wise_value"] = cpu["value"]
+            if cpu["row_wise_value"] > cpu["value"]:   # the baseline is the reference's faster layout
+                cpu["value"] = cpu["row_wise_value"]
+                cpu["sample"] = (f"same {n}x{N_FEAT} matrix and parameters, all host threads; the faster of the reference's two "
+                                 f"layouts: force_row_wise, 4 iterations after 1 warm-up (force_col_wise, whose model train_check "
+                                 f"compares: {k} iterations, col_wise_value)")
             ref.booster_free(rw)
         except Exception as ex:
             cpu["row_wise_value"] = None; cpu["row_wise_sample"] = str(ex)[:200]
