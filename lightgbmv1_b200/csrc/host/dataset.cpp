@@ -188,15 +188,29 @@ Dataset* Dataset::FromDenseMatrix(const void* data, int data_type, int32_t nrow,
   const int want = nrow < config.bin_construct_sample_cnt ? nrow : config.bin_construct_sample_cnt;
   const std::vector<int> sample = rand.Sample(nrow, want);
   const int sample_cnt = static_cast<int>(sample.size());
+  st.tick("sample indices");
   std::vector<std::vector<double>> sample_vals(ncol);
   std::vector<std::vector<int>> sample_idx(ncol);
-  // (column by column on the host threads: every column's lists come out in sample order, as in the reference's
-  // row-by-row loop)
+  // The sampled rows are first gathered into a compact [sample][column] block (each row of the user's matrix is
+  // touched once, by one thread), then every column's lists are cut from that block on the host threads -- in sample
+  // order, as the reference's row-by-row loop produces them.
+  std::unique_ptr<double[]> block;   // (not value-initialised: its pages are first touched by the threads that fill them)
+  if (row_major) {
+    block.reset(new double[static_cast<size_t>(sample_cnt) * ncol]);
+#pragma omp parallel for schedule(static)
+    for (int i = 0; i < sample_cnt; ++i) {
+      double* dst = block.get() + static_cast<size_t>(i) * ncol;
+      const size_t base = static_cast<size_t>(sample[i]) * ncol;
+      if (data_type == 0) { const float* src = static_cast<const float*>(data) + base; for (int c = 0; c < ncol; ++c) dst[c] = static_cast<double>(src[c]); }
+      else { const double* src = static_cast<const double*>(data) + base; for (int c = 0; c < ncol; ++c) dst[c] = src[c]; }
+    }
+  }
+  st.tick("sample gather");
 #pragma omp parallel for schedule(dynamic)
   for (int c = 0; c < ncol; ++c) {
     sample_vals[c].reserve(sample_cnt); sample_idx[c].reserve(sample_cnt);
     for (int i = 0; i < sample_cnt; ++i) {
-      const double v = M.at(sample[i], c);
+      const double v = row_major ? block[static_cast<size_t>(i) * ncol + c] : M.at(sample[i], c);
       if (std::fabs(v) > kZeroThreshold || std::isnan(v)) {
         sample_vals[c].push_back(v);
         sample_idx[c].push_back(i);
