@@ -125,7 +125,7 @@ int lgbcu_goss_apply(LgbCuContext* c, const uint32_t* inbag_bits, const uint32_t
   const int nblock = (c->N + BAG_BLOCK - 1) / BAG_BLOCK;
   if (!c->d_goss_amp) CU(dev_alloc(&c->d_goss_amp, (size_t)nblock * 32));
   if (!c->d_goss_mult || c->goss_mult_cap < nchunks) {
-    if (c->d_goss_mult) { cudaFree(c->d_goss_mult); c->d_goss_mult = nullptr; }
+    if (c->d_goss_mult) { lgb_dev_free(c->d_goss_mult); c->d_goss_mult = nullptr; }
     CU(dev_alloc(&c->d_goss_mult, (size_t)nchunks));
     c->goss_mult_cap = nchunks;
   }

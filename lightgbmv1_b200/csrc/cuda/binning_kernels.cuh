@@ -53,11 +53,11 @@ static bool pin_acquire(size_t bytes, void** out2) {
   std::lock_guard<std::mutex> lock(g_pin.mu);
   if (g_pin.busy) return false;
   if (g_pin.bytes < bytes) {
-    for (void*& q : g_pin.p) { if (q) cudaFreeHost(q); q = nullptr; }
+    for (void*& q : g_pin.p) { if (q) lgb_host_free(q); q = nullptr; }
     g_pin.bytes = 0;
-    if (cudaMallocHost(&g_pin.p[0], bytes) != cudaSuccess || cudaMallocHost(&g_pin.p[1], bytes) != cudaSuccess) {
+    if (lgb_host_malloc(&g_pin.p[0], bytes) != cudaSuccess || lgb_host_malloc(&g_pin.p[1], bytes) != cudaSuccess) {
       cudaGetLastError();
-      for (void*& q : g_pin.p) { if (q) cudaFreeHost(q); q = nullptr; }
+      for (void*& q : g_pin.p) { if (q) lgb_host_free(q); q = nullptr; }
       return false;
     }
     g_pin.bytes = bytes;
@@ -72,7 +72,7 @@ extern "C" {
 int lgbcu_binned_free(LgbCuBinnedMatrix* m) {
   if (!m) return 0;
   ScopedDevice dev_(m->device);
-  if (m->d_bins) cudaFree(m->d_bins);
+  if (m->d_bins) lgb_dev_free(m->d_bins);
   delete m;
   return 0;
 }
@@ -91,14 +91,22 @@ int lgbcu_bin_matrix(int device, const void* data, int data_type, int32_t nrow, 
     void* dev[4] = {nullptr, nullptr, nullptr, nullptr}; void* pin[2] = {nullptr, nullptr}; bool pin_cached = false;
     cudaStream_t s[2] = {nullptr, nullptr}; cudaEvent_t ev[2] = {nullptr, nullptr}; LgbCuBinnedMatrix* m = nullptr;
     ~Guard() {
-      for (void* p : dev) if (p) cudaFree(p);
-      if (pin_cached) pin_release(); else for (void* p : pin) if (p) cudaFreeHost(p);
+      for (void* p : dev) if (p) lgb_dev_free(p);
+      if (pin_cached) pin_release(); else for (void* p : pin) if (p) lgb_host_free(p);
       for (auto e : ev) if (e) cudaEventDestroy(e);
       for (auto st : s) if (st) cudaStreamDestroy(st);
       if (m) lgbcu_binned_free(m);
     }
   } G;
   const size_t esz = data_type == 0 ? 4 : 8;
+  const bool timing = std::getenv("LGBM_B200_TIMING") != nullptr;
+  auto t_prev = std::chrono::steady_clock::now();
+  auto tick = [&](const char* what) {
+    if (!timing) return;
+    const auto now = std::chrono::steady_clock::now();
+    std::fprintf(stderr, "[b200 timing]   bin_matrix: %-24s %8.2f ms\n", what, std::chrono::duration<double, std::milli>(now - t_prev).count());
+    t_prev = now;
+  };
   std::vector<BinFeatDev> hf(num_features);
   for (int f = 0; f < num_features; ++f) {
     NEED(feats[f].column >= 0 && feats[f].column < ncol && feats[f].num_bin >= 1 && feats[f].bound_offset >= 0 &&
@@ -106,16 +114,18 @@ int lgbcu_bin_matrix(int device, const void* data, int data_type, int32_t nrow, 
     hf[f] = BinFeatDev{feats[f].column, feats[f].num_bin, feats[f].most_freq_bin, feats[f].missing_type, feats[f].bound_offset, 0};
   }
   BinFeatDev* d_feats = nullptr; double* d_bounds = nullptr;
-  CU(cudaMalloc(&G.dev[0], sizeof(BinFeatDev) * num_features)); d_feats = static_cast<BinFeatDev*>(G.dev[0]);
-  CU(cudaMalloc(&G.dev[1], sizeof(double) * num_bounds)); d_bounds = static_cast<double*>(G.dev[1]);
+  CU(lgb_dev_malloc(&G.dev[0], sizeof(BinFeatDev) * num_features)); d_feats = static_cast<BinFeatDev*>(G.dev[0]);
+  CU(lgb_dev_malloc(&G.dev[1], sizeof(double) * num_bounds)); d_bounds = static_cast<double*>(G.dev[1]);
   CU(cudaMemcpy(d_feats, hf.data(), sizeof(BinFeatDev) * num_features, cudaMemcpyHostToDevice));
   CU(cudaMemcpy(d_bounds, upper_bounds, sizeof(double) * num_bounds, cudaMemcpyHostToDevice));
   G.m = new LgbCuBinnedMatrix();
   G.m->device = device; G.m->nrow = nrow; G.m->nfeat = num_features;
-  CU(cudaMalloc(reinterpret_cast<void**>(&G.m->d_bins), (size_t)nrow * num_features));
+  CU(lgb_dev_malloc(reinterpret_cast<void**>(&G.m->d_bins), (size_t)nrow * num_features));
   for (int i = 0; i < 2; ++i) { CU(cudaStreamCreateWithFlags(&G.s[i], cudaStreamNonBlocking)); CU(cudaEventCreateWithFlags(&G.ev[i], cudaEventDisableTiming)); }
-  cudaDeviceProp prop; CU(cudaGetDeviceProperties(&prop, device));
-  const int max_grid = prop.multiProcessorCount * 16;
+  tick("descriptors + result alloc");
+  int sm_count = 0;
+  CU(cudaDeviceGetAttribute(&sm_count, cudaDevAttrMultiProcessorCount, device));
+  const int max_grid = sm_count * 16;
   static const int hw = [] { const long n = sysconf(_SC_NPROCESSORS_ONLN); return n > 0 ? (int)n : 1; }();
   const int nthreads = std::max(omp_get_max_threads(), std::min(8, hw));
   if (is_row_major) {
@@ -123,7 +133,8 @@ int lgbcu_bin_matrix(int device, const void* data, int data_type, int32_t nrow, 
     const size_t row_bytes = (size_t)ncol * esz;
     const size_t chunk_rows = std::max<size_t>(1, std::min<size_t>((size_t)nrow, ((size_t)64 << 20) / row_bytes));
     G.pin_cached = pin_acquire(chunk_rows * row_bytes, G.pin);
-    for (int i = 0; i < 2; ++i) { if (!G.pin_cached) CU(cudaMallocHost(&G.pin[i], chunk_rows * row_bytes)); CU(cudaMalloc(&G.dev[2 + i], chunk_rows * row_bytes)); }
+    for (int i = 0; i < 2; ++i) { if (!G.pin_cached) CU(lgb_host_malloc(&G.pin[i], chunk_rows * row_bytes)); CU(lgb_dev_malloc(&G.dev[2 + i], chunk_rows * row_bytes)); }
+    tick("staging buffers");
     int k = 0;
     for (size_t r0 = 0; r0 < (size_t)nrow; r0 += chunk_rows, ++k) {
       const int b = k & 1;
@@ -151,7 +162,7 @@ int lgbcu_bin_matrix(int device, const void* data, int data_type, int32_t nrow, 
   } else {
     // column-major input: upload the used columns only, whole, then one launch
     const size_t col_bytes = (size_t)nrow * esz;
-    CU(cudaMalloc(&G.dev[2], col_bytes * num_features));
+    CU(lgb_dev_malloc(&G.dev[2], col_bytes * num_features));
     std::vector<BinFeatDev> hc = hf;
     for (int f = 0; f < num_features; ++f) {
       CU(cudaMemcpyAsync(static_cast<char*>(G.dev[2]) + f * col_bytes, static_cast<const char*>(data) + (size_t)hf[f].column * col_bytes,
@@ -166,8 +177,10 @@ int lgbcu_bin_matrix(int device, const void* data, int data_type, int32_t nrow, 
     g_launches.fetch_add(1, std::memory_order_relaxed);
     CU(cudaGetLastError());
   }
+  tick("chunks enqueued");
   CU(cudaStreamSynchronize(G.s[0]));
   CU(cudaStreamSynchronize(G.s[1]));
+  tick("drain");
   *out = G.m;
   G.m = nullptr;
   return 0;

@@ -2,12 +2,14 @@
 // See include/lgbcu.h for the contract of each entry point and the reference code it stands in for.
 #include <algorithm>
 #include <atomic>
+#include <chrono>
 #include <cmath>
 #include <cstddef>
 #include <cstdarg>
 #include <cstdio>
 #include <cstdlib>
 #include <cstring>
+#include <map>
 #include <mutex>
 #include <string>
 #include <vector>
@@ -71,11 +73,96 @@ struct ScopedDevice {
 
 #include "comm.cuh"
 
+// ---- allocation.  Boosters and datasets of the same shape are created and destroyed again and again in one process
+// (warm-up + timed run, cross-validation folds, parameter sweeps), and raw cudaMalloc / cudaFree / cudaMallocHost calls
+// are where their set-up time is lost -- and lost unpredictably: the same lgbcu_create took 6 ms or 165 ms on the same
+// box.  Device memory therefore comes from the device's stream-ordered pool with its release threshold raised, so
+// that freed blocks stay with the process and the next booster's allocations are pointer bumps; small page-locked
+// host buffers are kept on a size-keyed free list.  LGBCU_ALLOC_POOL=0 goes back to the plain calls.
+// Semantics are those of cudaMalloc / cudaFree: an allocation is usable on every stream when the call returns, a free
+// waits for the device first (the callers rely on both).
+static bool pool_enabled() {
+  static const bool on = [] { const char* e = std::getenv("LGBCU_ALLOC_POOL"); return !(e && std::atoi(e) == 0); }();
+  return on;
+}
+static bool pool_ready(int dev) {
+  static std::mutex mu; static int state[64] = {0};   // 0 unknown, 1 pool, -1 no pool
+  if (dev < 0 || dev >= 64) return false;
+  std::lock_guard<std::mutex> lock(mu);
+  if (state[dev] == 0) {
+    int ok = 0; cudaMemPool_t pool = nullptr;
+    if (cudaDeviceGetAttribute(&ok, cudaDevAttrMemoryPoolsSupported, dev) == cudaSuccess && ok &&
+        cudaDeviceGetDefaultMemPool(&pool, dev) == cudaSuccess) {
+      unsigned long long keep = ~0ull;
+      state[dev] = cudaMemPoolSetAttribute(pool, cudaMemPoolAttrReleaseThreshold, &keep) == cudaSuccess ? 1 : -1;
+    } else {
+      state[dev] = -1;
+    }
+    cudaGetLastError();
+  }
+  return state[dev] == 1;
+}
+static cudaError_t lgb_dev_malloc(void** p, size_t bytes) {
+  int dev = 0;
+  if (pool_enabled() && cudaGetDevice(&dev) == cudaSuccess && pool_ready(dev)) {
+    const cudaError_t e = cudaMallocAsync(p, bytes, cudaStreamPerThread);
+    if (e != cudaSuccess) return e;
+    return cudaStreamSynchronize(cudaStreamPerThread);
+  }
+  return cudaMalloc(p, bytes);
+}
+template <typename T>
+static cudaError_t lgb_dev_malloc(T** p, size_t bytes) { return lgb_dev_malloc(reinterpret_cast<void**>(p), bytes); }
+static cudaError_t lgb_dev_free(void* p) {
+  if (!p) return cudaSuccess;
+  int dev = 0;
+  if (pool_enabled() && cudaGetDevice(&dev) == cudaSuccess && pool_ready(dev)) {
+    cudaDeviceSynchronize();
+    return cudaFreeAsync(p, cudaStreamPerThread);
+  }
+  return cudaFree(p);
+}
+struct HostCache {
+  std::mutex mu; std::multimap<size_t, void*> free_; std::map<void*, size_t> live; size_t cached = 0;
+};
+static HostCache g_host;
+static cudaError_t lgb_host_malloc(void** p, size_t bytes) {
+  if (pool_enabled()) {
+    std::lock_guard<std::mutex> lock(g_host.mu);
+    auto it = g_host.free_.find(bytes);
+    if (it != g_host.free_.end()) {
+      *p = it->second; g_host.free_.erase(it); g_host.cached -= bytes; g_host.live[*p] = bytes;
+      return cudaSuccess;
+    }
+  }
+  const cudaError_t e = cudaMallocHost(p, bytes);
+  if (e == cudaSuccess && pool_enabled()) { std::lock_guard<std::mutex> lock(g_host.mu); g_host.live[*p] = bytes; }
+  return e;
+}
+template <typename T>
+static cudaError_t lgb_host_malloc(T** p, size_t bytes) { return lgb_host_malloc(reinterpret_cast<void**>(p), bytes); }
+static cudaError_t lgb_host_free(void* p) {
+  if (!p) return cudaSuccess;
+  if (pool_enabled()) {
+    std::lock_guard<std::mutex> lock(g_host.mu);
+    auto it = g_host.live.find(p);
+    if (it != g_host.live.end()) {
+      const size_t bytes = it->second;
+      g_host.live.erase(it);
+      if (bytes <= ((size_t)64 << 20) && g_host.cached + bytes <= ((size_t)512 << 20)) {
+        g_host.free_.emplace(bytes, p); g_host.cached += bytes;
+        return cudaSuccess;
+      }
+    }
+  }
+  return cudaFreeHost(p);
+}
+
 template <typename T>
 cudaError_t dev_alloc(T** p, size_t n) {
-  if (*p) { cudaFree(*p); *p = nullptr; }
+  if (*p) { lgb_dev_free(*p); *p = nullptr; }
   if (n == 0) n = 1;
-  return cudaMalloc(reinterpret_cast<void**>(p), n * sizeof(T));
+  return lgb_dev_malloc(reinterpret_cast<void**>(p), n * sizeof(T));
 }
 
 }  // namespace
@@ -263,8 +350,8 @@ int ensure_tree_buffers(LgbCuContext* c) {
   CU(cudaMemsetAsync(c->d_expanded, 0, sizeof(int) * (size_t)L, c->stream));
   CU(dev_alloc(&c->d_records, (size_t)L));
   CU(dev_alloc(&c->d_leaf_value, (size_t)L));
-  if (c->h_records) cudaFreeHost(c->h_records);
-  CU(cudaMallocHost(reinterpret_cast<void**>(&c->h_records), sizeof(LgbCuSplitRecord) * (size_t)L));
+  if (c->h_records) lgb_host_free(c->h_records);
+  CU(lgb_host_malloc(reinterpret_cast<void**>(&c->h_records), sizeof(LgbCuSplitRecord) * (size_t)L));
   CU(cudaMemsetAsync(c->d_splittable, 0, slots * c->F, c->stream));
   c->alloc_lookahead = K;
   c->alloc_leaves = L;
@@ -378,7 +465,7 @@ int setup_ownership(LgbCuContext* c) {
   }
   c->own_begin[c->world] = c->F;
   if (!c->d_cand_send) CU(dev_alloc(&c->d_cand_send, (size_t)2 * LGB_KMAX));
-  if (c->d_cand_all) { cudaFree(c->d_cand_all); c->d_cand_all = nullptr; }
+  if (c->d_cand_all) { lgb_dev_free(c->d_cand_all); c->d_cand_all = nullptr; }
   CU(dev_alloc(&c->d_cand_all, (size_t)c->world * 2 * LGB_KMAX));
   return 0;
 }
@@ -459,18 +546,18 @@ int lgbcu_create(int device_id, LgbCuContext** out) {
   LgbCuContext* c = new LgbCuContext();
   struct Guard { LgbCuContext* c; ~Guard() { if (c) lgbcu_destroy(c); } } guard{c};   // a failure below frees the half-built context
   c->device = device_id;
-  cudaDeviceProp prop;
-  CU(cudaGetDeviceProperties(&prop, device_id));
-  c->num_sms = prop.multiProcessorCount;
+  int sm_count = 0;
+  CU(cudaDeviceGetAttribute(&sm_count, cudaDevAttrMultiProcessorCount, device_id));  // (cudaGetDeviceProperties costs milliseconds)
+  c->num_sms = sm_count;
   if (const char* e = std::getenv("LGBCU_HIST_MIN_ROWS")) { const int v = std::atoi(e); if (v >= 1) c->hist_min_rows = v; }
   if (const char* e = std::getenv("LGBCU_DP_OWNERSHIP")) c->dp_owner_cfg = std::atoi(e) != 0 ? 1 : 0;
   if (const char* e = std::getenv("LGBCU_HIST_SMALL_ROWS")) { const int v = std::atoi(e); if (v >= 0) c->hist_small_rows = v; }
   CU(cudaStreamCreateWithFlags(&c->stream, cudaStreamNonBlocking));
   CU(dev_alloc(&c->d_ctl, 1));
   CU(cudaMemset(c->d_ctl, 0, sizeof(DevCtl)));
-  CU(cudaMallocHost(reinterpret_cast<void**>(&c->h_ctl), sizeof(DevCtl)));
-  CU(cudaMallocHost(reinterpret_cast<void**>(&c->h_leaf), sizeof(DevLeaf)));
-  CU(cudaMallocHost(reinterpret_cast<void**>(&c->h_split), sizeof(DevSplit)));
+  CU(lgb_host_malloc(reinterpret_cast<void**>(&c->h_ctl), sizeof(DevCtl)));
+  CU(lgb_host_malloc(reinterpret_cast<void**>(&c->h_leaf), sizeof(DevLeaf)));
+  CU(lgb_host_malloc(reinterpret_cast<void**>(&c->h_split), sizeof(DevSplit)));
   CU(cudaFuncSetAttribute(k_hist, cudaFuncAttributeMaxDynamicSharedMemorySize, HIST_SMEM_BYTES));
   {
     // the histogram kernel is persistent over its work units: as many clusters as the GPU can hold at once
@@ -524,12 +611,12 @@ int lgbcu_destroy(LgbCuContext* c) {
                   c->d_tree_f64, c->d_rows, c->d_scratch, c->d_parent_split, c->d_mfb_fix, c->d_feat_key, c->d_leaf_key, c->d_spec, c->d_expanded,
                   c->d_bag_state, c->d_bag_bits, c->d_bag_tile, c->d_bag_ctl, c->d_bag, c->d_goss, c->d_goss_amp, c->d_goss_mult,
                   c->d_cand_send, c->d_cand_all};
-  for (void* p : ptrs) if (p) cudaFree(p);
-  if (c->h_records) cudaFreeHost(c->h_records);
-  if (c->h_ctl) cudaFreeHost(c->h_ctl);
-  if (c->h_leaf) cudaFreeHost(c->h_leaf);
-  if (c->h_split) cudaFreeHost(c->h_split);
-  for (int i = 0; i < 2; ++i) { if (c->h_stage[i]) cudaFreeHost(c->h_stage[i]); if (c->stage_ev[i]) cudaEventDestroy(c->stage_ev[i]); }
+  for (void* p : ptrs) if (p) lgb_dev_free(p);
+  if (c->h_records) lgb_host_free(c->h_records);
+  if (c->h_ctl) lgb_host_free(c->h_ctl);
+  if (c->h_leaf) lgb_host_free(c->h_leaf);
+  if (c->h_split) lgb_host_free(c->h_split);
+  for (int i = 0; i < 2; ++i) { if (c->h_stage[i]) lgb_host_free(c->h_stage[i]); if (c->stage_ev[i]) cudaEventDestroy(c->stage_ev[i]); }
   for (auto e : c->ev) cudaEventDestroy(e);
   if (c->stream) cudaStreamDestroy(c->stream);
   delete c;
@@ -606,7 +693,7 @@ int lgbcu_set_dataset(LgbCuContext* c, int32_t num_data, int32_t num_features, c
   {
     // one contiguous H2D copy, then pad rows to the 16-byte stride on the device (a strided 2-D copy of 28-byte rows
     // crawls: one DMA descriptor per row)
-    struct Tmp { uint8_t* p = nullptr; ~Tmp() { if (p) cudaFree(p); } } packed;   // released on every way out
+    struct Tmp { uint8_t* p = nullptr; ~Tmp() { if (p) lgb_dev_free(p); } } packed;   // released on every way out
     CU(dev_alloc(&packed.p, (size_t)num_data * num_features));
     CU(cudaMemcpyAsync(packed.p, bins, (size_t)num_data * num_features, cudaMemcpyHostToDevice, c->stream));
     LAUNCH(k_pad_rows, grid_for(c, (long long)num_data * (c->stride / 4), 256), 256, 0, c->stream, (long long)num_data,
@@ -627,7 +714,7 @@ int lgbcu_set_dataset_columns(LgbCuContext* c, int32_t num_data, int32_t num_fea
   USE_DEVICE(c->device);
   if (setup_dataset_common(c, num_data, num_features, meta)) return -1;
   CU(cudaMemsetAsync(c->d_bins, 0, (size_t)num_data * c->stride, c->stream));
-  struct Tmp { uint8_t* p[2] = {nullptr, nullptr}; ~Tmp() { for (auto q : p) if (q) cudaFree(q); } } T;   // released on every way out
+  struct Tmp { uint8_t* p[2] = {nullptr, nullptr}; ~Tmp() { for (auto q : p) if (q) lgb_dev_free(q); } } T;   // released on every way out
   uint8_t** tmp = T.p;
   CU(dev_alloc(&tmp[0], (size_t)num_data));
   CU(dev_alloc(&tmp[1], (size_t)num_data));
@@ -815,7 +902,7 @@ int lgbcu_copy_score(LgbCuContext* c, double* score, int32_t n) {
   }
   if (!c->h_stage[0]) {
     for (int i = 0; i < 2; ++i) {
-      CU(cudaMallocHost(reinterpret_cast<void**>(&c->h_stage[i]), CH * sizeof(double)));
+      CU(lgb_host_malloc(reinterpret_cast<void**>(&c->h_stage[i]), CH * sizeof(double)));
       CU(cudaEventCreateWithFlags(&c->stage_ev[i], cudaEventDisableTiming));
     }
   }

@@ -203,8 +203,8 @@ int rank_prepare(LgbCuContext* c) {
   double* d_table = nullptr; double* d_disc = nullptr;
   CU(dev_alloc(&c->d_inv_max_dcg, inv.size()));
   CU(cudaMemcpy(c->d_inv_max_dcg, inv.data(), sizeof(double) * inv.size(), cudaMemcpyHostToDevice));
-  if (c->d_sigmoid_table) { cudaFree(c->d_sigmoid_table); c->d_sigmoid_table = nullptr; }
-  CU(cudaMalloc(reinterpret_cast<void**>(&d_table), sizeof(double) * (RANK_SIGMOID_BINS + RANK_MAX_POSITION)));
+  if (c->d_sigmoid_table) { lgb_dev_free(c->d_sigmoid_table); c->d_sigmoid_table = nullptr; }
+  CU(lgb_dev_malloc(reinterpret_cast<void**>(&d_table), sizeof(double) * (RANK_SIGMOID_BINS + RANK_MAX_POSITION)));
   d_disc = d_table + RANK_SIGMOID_BINS;
   CU(cudaMemcpy(d_table, table.data(), sizeof(double) * RANK_SIGMOID_BINS, cudaMemcpyHostToDevice));
   CU(cudaMemcpy(d_disc, discount.data(), sizeof(double) * RANK_MAX_POSITION, cudaMemcpyHostToDevice));

@@ -20,22 +20,22 @@ int upload_vec(LgbCuContext* c, T** dst, const T* src, size_t n) {
 
 void free_ndcg(NdcgTables* t) {
   void* p[] = {t->d_eval_at, t->d_inv_max_dcg, t->d_query_weight, t->d_label_gain, t->d_discount};
-  for (void* q : p) if (q) cudaFree(q);
+  for (void* q : p) if (q) lgb_dev_free(q);
   *t = NdcgTables();
 }
 
 void free_valid_sets(LgbCuContext* c) {
   for (ValidSet& v : c->valid) {
     void* p[] = {v.d_bins, v.d_score, v.d_label, v.d_weight, v.d_query};
-    for (void* q : p) if (q) cudaFree(q);
+    for (void* q : p) if (q) lgb_dev_free(q);
     free_ndcg(&v.ndcg);
   }
   c->valid.clear();
   free_ndcg(&c->train_ndcg);
   void* p[] = {c->d_eval_partial, c->d_eval_out, c->d_auc_keys[0], c->d_auc_keys[1], c->d_auc_vals[0], c->d_auc_vals[1],
                c->d_auc_pos, c->d_auc_groups, c->d_cub_tmp, c->d_ndcg_per_query};
-  for (void* q : p) if (q) cudaFree(q);
-  if (c->h_eval_out) cudaFreeHost(c->h_eval_out);
+  for (void* q : p) if (q) lgb_dev_free(q);
+  if (c->h_eval_out) lgb_host_free(c->h_eval_out);
   c->d_eval_partial = c->d_eval_out = c->d_auc_pos = c->d_ndcg_per_query = nullptr; c->h_eval_out = nullptr;
   c->d_auc_keys[0] = c->d_auc_keys[1] = nullptr; c->d_auc_vals[0] = c->d_auc_vals[1] = nullptr;
   c->d_auc_groups = nullptr; c->d_cub_tmp = nullptr; c->cub_tmp_bytes = 0; c->auc_cap = 0; c->ndcg_cap = 0;
@@ -52,7 +52,7 @@ int lgbcu_valid_create(LgbCuContext* c, int32_t num_data, const uint8_t* bins, i
   v.n = num_data;
   CU(dev_alloc(&v.d_bins, (size_t)num_data * c->stride));
   {
-    struct Tmp { uint8_t* p = nullptr; ~Tmp() { if (p) cudaFree(p); } } packed;   // released on every way out
+    struct Tmp { uint8_t* p = nullptr; ~Tmp() { if (p) lgb_dev_free(p); } } packed;   // released on every way out
     CU(dev_alloc(&packed.p, (size_t)num_data * c->F));
     CU(cudaMemcpyAsync(packed.p, bins, (size_t)num_data * c->F, cudaMemcpyHostToDevice, c->stream));
     LAUNCH(k_pad_rows, grid_for(c, (long long)num_data * (c->stride / 4), 256), 256, 0, c->stream, (long long)num_data,
@@ -173,7 +173,7 @@ int eval_scratch(LgbCuContext* c) {
   if (!c->d_eval_partial) {
     CU(dev_alloc(&c->d_eval_partial, (size_t)EVAL_MAX_BLOCKS * 2));
     CU(dev_alloc(&c->d_eval_out, (size_t)64));
-    CU(cudaMallocHost(reinterpret_cast<void**>(&c->h_eval_out), sizeof(double) * 64));
+    CU(lgb_host_malloc(reinterpret_cast<void**>(&c->h_eval_out), sizeof(double) * 64));
   }
   return 0;
 }
@@ -204,9 +204,9 @@ int eval_auc(LgbCuContext* c, int n, const double* score, const float* label, co
   CU(cub::DeviceScan::InclusiveSum(nullptr, b2, c->d_auc_pos, c->d_auc_pos, n, c->stream));
   const size_t need = std::max(b0, std::max(b1, b2));
   if (c->cub_tmp_bytes < need) {
-    if (c->d_cub_tmp) cudaFree(c->d_cub_tmp);
+    if (c->d_cub_tmp) lgb_dev_free(c->d_cub_tmp);
     c->d_cub_tmp = nullptr;
-    CU(cudaMalloc(&c->d_cub_tmp, need));
+    CU(lgb_dev_malloc(&c->d_cub_tmp, need));
     c->cub_tmp_bytes = need;
   }
   size_t tb = c->cub_tmp_bytes;

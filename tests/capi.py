@@ -66,8 +66,11 @@ class LGBMLib:
                                                             h.ctypes.data_as(C.POINTER(C.c_float)), C.byref(fin)))
         return fin.value
 
-    def get_predict(self, b, n, data_idx=0):
-        out = np.empty(n, dtype=np.float64)
+    def get_predict(self, b, n, data_idx=0, out=None):
+        """`out`: a caller-owned float64 buffer of n entries (e.g. one whose pages are already mapped)"""
+        if out is None:
+            out = np.empty(n, dtype=np.float64)
+        assert out.dtype == np.float64 and out.size == n and out.flags.c_contiguous
         ln = C.c_int64(0)
         self.check(self.lib.LGBM_BoosterGetPredict(b, C.c_int(data_idx), C.byref(ln), out.ctypes.data_as(C.POINTER(C.c_double))))
         assert ln.value == n
