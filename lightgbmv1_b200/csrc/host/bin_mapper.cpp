@@ -1,6 +1,8 @@
 #include "bin_mapper.h"
 
 #include <algorithm>
+#include <cstdint>
+#include <cstring>
 #include <iomanip>
 
 namespace lgb {
@@ -121,6 +123,34 @@ bool NoUsefulSplit(const std::vector<int>& cnt_in_bin, int total_cnt, int filter
   return true;
 }
 
+// Ascending sort of finite doubles (NaNs are removed before; zeros never reach FindBin, so -0.0 / +0.0 cannot be
+// told apart by it).  Equal doubles are indistinguishable, so any correct sort gives the array the reference's
+// std::stable_sort gives; an LSD radix sort over the order-preserving integer image is ~6x faster on the 200K-value
+// samples this runs on, once per feature.
+void SortDoubles(std::vector<double>* values) {
+  const size_t n = values->size();
+  if (n < 8192) { std::sort(values->begin(), values->end()); return; }
+  std::vector<uint64_t> a(n), b(n);
+  for (size_t i = 0; i < n; ++i) {
+    uint64_t u; std::memcpy(&u, &(*values)[i], 8);
+    a[i] = u ^ ((u >> 63) ? ~0ull : 0x8000000000000000ull);
+  }
+  std::vector<uint32_t> count(65536);
+  for (int pass = 0; pass < 4; ++pass) {
+    const int shift = 16 * pass;
+    std::fill(count.begin(), count.end(), 0u);
+    for (size_t i = 0; i < n; ++i) ++count[(a[i] >> shift) & 0xffffu];
+    uint32_t run = 0;
+    for (uint32_t& c : count) { const uint32_t t = c; c = run; run += t; }
+    for (size_t i = 0; i < n; ++i) b[count[(a[i] >> shift) & 0xffffu]++] = a[i];
+    a.swap(b);
+  }
+  for (size_t i = 0; i < n; ++i) {
+    const uint64_t u = a[i] ^ ((a[i] >> 63) ? 0x8000000000000000ull : ~0ull);
+    std::memcpy(&(*values)[i], &u, 8);
+  }
+}
+
 }  // namespace
 
 void BinMapper::FindBin(std::vector<double> values, size_t total_sample_cnt, int max_bin, int min_data_in_bin,
@@ -139,7 +169,7 @@ void BinMapper::FindBin(std::vector<double> values, size_t total_sample_cnt, int
   default_bin_ = 0;
   const int zero_cnt = static_cast<int>(total_sample_cnt - num_sample - na_cnt);
 
-  std::stable_sort(values.begin(), values.end());
+  SortDoubles(&values);
   // distinct values with counts; the implied zeros are spliced in at their sorted position
   std::vector<double> dv;
   std::vector<int> dc;
