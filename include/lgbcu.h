@@ -43,7 +43,7 @@ typedef struct LgbCuContext LgbCuContext;
 /* missing_type values: include/LightGBM/bin.h (enum MissingType { None, Zero, NaN }) */
 enum { LGBCU_MISSING_NONE = 0, LGBCU_MISSING_ZERO = 1, LGBCU_MISSING_NAN = 2 };
 /* objective kinds implemented on device (src/objective/) */
-enum { LGBCU_OBJ_NONE = 0, LGBCU_OBJ_BINARY = 1, LGBCU_OBJ_L2 = 2, LGBCU_OBJ_LAMBDARANK = 3 };
+enum { LGBCU_OBJ_NONE = 0, LGBCU_OBJ_BINARY = 1, LGBCU_OBJ_L2 = 2, LGBCU_OBJ_LAMBDARANK = 3, LGBCU_OBJ_MULTICLASS = 4 };
 /* histogram kernel selection (LGBCU_HIST_AUTO picks by leaf size) */
 enum { LGBCU_HIST_AUTO = 0, LGBCU_HIST_GLOBAL_ATOMIC = 1, LGBCU_HIST_WARP_PRIVATE = 2 };
 
@@ -167,8 +167,18 @@ LGBCU_API int lgbcu_set_query(LgbCuContext* ctx, const int32_t* boundaries, int3
  * binary (src/objective/binary_objective.hpp:102-133): p0 = sigmoid, p1 = label_weight[neg], p2 = label_weight[pos]
  * l2     (src/objective/regression_objective.hpp:125-140): no params
  * lambdarank (src/objective/rank_objective.hpp:48-65,139-229): p0 = sigmoid, p1 = truncation_level, p2 = norm(0/1);
- *        label_gain via lgbcu_set_label_gain */
+ *        label_gain via lgbcu_set_label_gain
+ * multiclass (src/objective/multiclass_objective.hpp:86-130, softmax): p0 = num_class, p1 = factor = K / (K - 1);
+ *        fills all K gradient / hessian planes from all K score planes in one pass */
 LGBCU_API int lgbcu_set_objective(LgbCuContext* ctx, int kind, double p0, double p1, double p2);
+/* Multiclass: the learner keeps num_class planes of scores, gradients and hessians ([class][row], the reference's
+ * ScoreUpdater / gradients_ layout; validation sets likewise).  lgbcu_set_class picks the plane that every other call
+ * -- lgbcu_begin_tree / lgbcu_train_tree, the lgbcu_add_score_* family, lgbcu_copy_score, lgbcu_set_gradients, the
+ * validation-set calls -- works on, so one tree per class and iteration is grown exactly as a single-class tree is
+ * (GBDT::TrainOneIter's loop over cur_tree_id, src/boosting/gbdt.cpp:353-412).  Set the number of classes before any
+ * validation set is added. */
+LGBCU_API int lgbcu_set_num_class(LgbCuContext* ctx, int32_t num_class);
+LGBCU_API int lgbcu_set_class(LgbCuContext* ctx, int32_t class_id);
 LGBCU_API int lgbcu_set_label_gain(LgbCuContext* ctx, const double* label_gain, int32_t n);
 LGBCU_API int lgbcu_get_gradients(LgbCuContext* ctx);                      /* score -> grad,hess (device) */
 LGBCU_API int lgbcu_set_gradients(LgbCuContext* ctx, const float* grad, const float* hess, int32_t n);
@@ -310,6 +320,8 @@ LGBCU_API int lgbcu_valid_copy_score(LgbCuContext* ctx, int32_t set, double* out
 #define LGBCU_METRIC_BINARY_LOGLOSS 2
 #define LGBCU_METRIC_AUC 3
 #define LGBCU_METRIC_NDCG 4
+#define LGBCU_METRIC_MULTI_LOGLOSS 5   /* `sigmoid` > 0: softmax the K raw scores first (the objective's ConvertOutput) */
+#define LGBCU_METRIC_MULTI_ERROR 6     /* `sigmoid` = +top_k (softmax first) or -top_k (scores as they are) */
 LGBCU_API int lgbcu_eval_set_ndcg(LgbCuContext* ctx, int32_t set, const int32_t* eval_at, int32_t num_eval,
                                   const double* inv_max_dcg, const float* query_weight, const double* label_gain,
                                   int32_t num_label_gain, const double* discount, int32_t num_discount);

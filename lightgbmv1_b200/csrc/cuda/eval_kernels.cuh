@@ -55,6 +55,41 @@ __global__ void __launch_bounds__(EVAL_THREADS) k_eval_pointwise(int n, int kind
   if (threadIdx.x == 0) partial[blockIdx.x] = t;
 }
 
+// Multiclass metrics (src/metric/multiclass_metric.hpp:60-120): the K raw scores of a row ([class][row] planes) are
+// converted by the objective's softmax (softmax = 0: no objective, the scores are taken as they are), then
+// kind 0: multi_logloss  -log(max(p[label], kEpsilon))          (MultiSoftmaxLoglossMetric::LossOnPoint, :167-175)
+// kind 1: multi_error@top_k: 1 if more than top_k classes score >= the label's class   (MultiErrorMetric, :142-151)
+__global__ void __launch_bounds__(EVAL_THREADS) k_eval_multiclass(int n, int K, int kind, int top_k, int softmax,
+                                                                  const double* __restrict__ score, const float* __restrict__ label,
+                                                                  const float* __restrict__ weight, double* __restrict__ partial) {
+  __shared__ double s_warp[EVAL_THREADS / 32];
+  double acc = 0.0;
+  for (int i = blockIdx.x * blockDim.x + threadIdx.x; i < n; i += gridDim.x * blockDim.x) {
+    const int lab = (int)label[i];
+    double wmax = score[i];
+    for (int k = 1; k < K; ++k) wmax = fmax(score[(size_t)n * k + i], wmax);
+    double wsum = 0.0;
+    if (softmax) for (int k = 0; k < K; ++k) wsum += exp(score[(size_t)n * k + i] - wmax);
+    const double raw_l = score[(size_t)n * lab + i];
+    const double pl = softmax ? exp(raw_l - wmax) / wsum : raw_l;
+    double loss;
+    if (kind == 0) {
+      loss = pl > LGB_EPS ? -log(pl) : -log(LGB_EPS);
+    } else {
+      int num_larger = 0;
+      for (int k = 0; k < K; ++k) {
+        const double raw = score[(size_t)n * k + i];
+        const double pk = softmax ? exp(raw - wmax) / wsum : raw;
+        if (pk >= pl) ++num_larger;
+      }
+      loss = num_larger > top_k ? 1.0 : 0.0;
+    }
+    acc += weight ? loss * weight[i] : loss;
+  }
+  const double t = block_sum_f64(acc, s_warp);
+  if (threadIdx.x == 0) partial[blockIdx.x] = t;
+}
+
 __global__ void __launch_bounds__(EVAL_THREADS) k_sum_f32(int n, const float* __restrict__ v, double* __restrict__ partial) {
   __shared__ double s_warp[EVAL_THREADS / 32];
   double acc = 0.0;

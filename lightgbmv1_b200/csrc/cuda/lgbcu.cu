@@ -183,7 +183,8 @@ struct NdcgTables {
 struct ValidSet {
   int n = 0;
   uint8_t* d_bins = nullptr;   // row-major, same stride as the training matrix
-  double* d_score = nullptr;
+  double* d_score = nullptr;        // the current class's plane of d_score_base
+  double* d_score_base = nullptr;   // [num_class][n]
   float* d_label = nullptr; float* d_weight = nullptr;
   int* d_query = nullptr; int num_queries = 0;
   NdcgTables ndcg;
@@ -215,6 +216,11 @@ struct LgbCuContext {
   // per-row state
   float2* d_gh = nullptr;  // interleaved (g, h) of the current iteration
   float *d_grad = nullptr, *d_hess = nullptr, *d_label = nullptr, *d_weight = nullptr;
+  // multiclass: K score / gradient / hessian planes ([class][row], as the reference's ScoreUpdater and gradients_ lay
+  // them out); d_score / d_grad / d_hess always point at the CURRENT class's plane (lgbcu_set_class), so that every
+  // kernel below trains and scores "a" class without knowing there are several
+  int num_class = 1, cur_class = 0;
+  float *d_grad_base = nullptr, *d_hess_base = nullptr; double* d_score_base = nullptr;
   bool has_weight = false, has_label = false;
   double* d_score = nullptr;
   int* d_indices[2] = {nullptr, nullptr};
@@ -604,7 +610,7 @@ int lgbcu_destroy(LgbCuContext* c) {
   drop_graph(c);
   lgbcu_comm_destroy(c);
   free_valid_sets(c);
-  void* ptrs[] = {c->d_bins, c->d_feats, c->d_feat_used, c->d_grad, c->d_hess, c->d_gh, c->d_label, c->d_weight, c->d_score,
+  void* ptrs[] = {c->d_bins, c->d_feats, c->d_feat_used, c->d_grad_base, c->d_hess_base, c->d_gh, c->d_label, c->d_weight, c->d_score_base,
                   c->d_indices[0], c->d_indices[1], c->d_part_bits, c->d_part_sync, c->d_bins_col, c->d_query, c->d_label_gain,
                   c->d_inv_max_dcg, c->d_sigmoid_table, c->d_pool, c->d_splittable, c->d_leaves, c->d_best,
                   c->d_feat_best, c->d_ctl, c->d_records, c->d_leaf_value, c->d_export, c->d_tree_i32, c->d_tree_i8,
@@ -664,11 +670,12 @@ static int setup_dataset_common(LgbCuContext* c, int32_t num_data, int32_t num_f
   CU(dev_alloc(&c->d_feat_key, (size_t)2 * LGB_KMAX * num_features));
   CU(dev_alloc(&c->d_parent_split, (size_t)LGB_KMAX * num_features));
   CU(cudaMemsetAsync(c->d_parent_split, 1, (size_t)LGB_KMAX * num_features, c->stream));
-  CU(dev_alloc(&c->d_grad, (size_t)num_data));
-  CU(dev_alloc(&c->d_hess, (size_t)num_data));
+  CU(dev_alloc(&c->d_grad_base, (size_t)num_data * c->num_class));
+  CU(dev_alloc(&c->d_hess_base, (size_t)num_data * c->num_class));
   CU(dev_alloc(&c->d_gh, (size_t)num_data));
-  CU(dev_alloc(&c->d_score, (size_t)num_data));
-  CU(cudaMemsetAsync(c->d_score, 0, sizeof(double) * num_data, c->stream));
+  CU(dev_alloc(&c->d_score_base, (size_t)num_data * c->num_class));
+  CU(cudaMemsetAsync(c->d_score_base, 0, sizeof(double) * num_data * c->num_class, c->stream));
+  c->cur_class = 0; c->d_grad = c->d_grad_base; c->d_hess = c->d_hess_base; c->d_score = c->d_score_base;
   CU(dev_alloc(&c->d_indices[0], (size_t)num_data));
   CU(dev_alloc(&c->d_indices[1], (size_t)num_data));
   const size_t ntiles = ((size_t)num_data + PART_TILE - 1) / PART_TILE;
@@ -795,7 +802,7 @@ int lgbcu_set_query(LgbCuContext* c, const int32_t* boundaries, int32_t num_quer
 
 int lgbcu_set_objective(LgbCuContext* c, int kind, double p0, double p1, double p2) {
   NEED(c, "lgbcu: NULL context");
-  NEED(kind >= LGBCU_OBJ_NONE && kind <= LGBCU_OBJ_LAMBDARANK, "lgbcu_set_objective: unknown kind %d", kind);
+  NEED(kind >= LGBCU_OBJ_NONE && kind <= LGBCU_OBJ_MULTICLASS, "lgbcu_set_objective: unknown kind %d", kind);
   if (kind == LGBCU_OBJ_BINARY || kind == LGBCU_OBJ_LAMBDARANK) NEED(p0 > 0, "Sigmoid parameter %f should be greater than zero", p0);
   c->objective = kind; c->obj_p[0] = p0; c->obj_p[1] = p1; c->obj_p[2] = p2;
   c->rank_ready = false;
@@ -812,6 +819,35 @@ int lgbcu_set_label_gain(LgbCuContext* c, const double* label_gain, int32_t n) {
   return 0;
 }
 
+// Multiclass: K planes of scores / gradients / hessians.  Call before the dataset is set (or the planes are rebuilt,
+// zeroed).  lgbcu_set_class picks the plane every later call trains / scores / reads.
+int lgbcu_set_num_class(LgbCuContext* c, int32_t num_class) {
+  NEED(c && num_class >= 1 && num_class <= 4096, "lgbcu_set_num_class: bad argument");
+  if (num_class == c->num_class) return 0;
+  USE_DEVICE(c->device);
+  c->num_class = num_class; c->cur_class = 0;
+  if (c->N > 0) {
+    CU(dev_alloc(&c->d_grad_base, (size_t)c->N * num_class));
+    CU(dev_alloc(&c->d_hess_base, (size_t)c->N * num_class));
+    CU(dev_alloc(&c->d_score_base, (size_t)c->N * num_class));
+    CU(cudaMemsetAsync(c->d_score_base, 0, sizeof(double) * (size_t)c->N * num_class, c->stream));
+    c->d_grad = c->d_grad_base; c->d_hess = c->d_hess_base; c->d_score = c->d_score_base;
+  }
+  NEED(c->valid.empty(), "lgbcu_set_num_class: validation sets were added before the number of classes was known");
+  return 0;
+}
+
+int lgbcu_set_class(LgbCuContext* c, int32_t k) {
+  NEED(c && k >= 0 && k < c->num_class, "lgbcu_set_class: class %d out of range", (int)k);
+  c->cur_class = k;
+  if (c->N > 0) {
+    c->d_grad = c->d_grad_base + (size_t)k * c->N; c->d_hess = c->d_hess_base + (size_t)k * c->N;
+    c->d_score = c->d_score_base + (size_t)k * c->N;
+  }
+  for (ValidSet& v : c->valid) v.d_score = v.d_score_base + (size_t)k * v.n;
+  return 0;
+}
+
 int lgbcu_get_gradients(LgbCuContext* c) {
   NEED(c && c->N > 0, "lgbcu_get_gradients: dataset not set");
   NEED(c->has_label, "lgbcu_get_gradients: label not set");
@@ -825,6 +861,9 @@ int lgbcu_get_gradients(LgbCuContext* c) {
   } else if (c->objective == LGBCU_OBJ_LAMBDARANK) {
     if (rank_prepare(c)) return -1;
     if (rank_launch(c)) return -1;
+  } else if (c->objective == LGBCU_OBJ_MULTICLASS) {
+    NEED((int)c->obj_p[0] == c->num_class, "lgbcu_get_gradients: the objective has %d classes, the learner %d (lgbcu_set_num_class)", (int)c->obj_p[0], c->num_class);
+    LAUNCH(k_grad_multiclass, g, 256, 0, c->stream, c->N, c->num_class, c->d_score_base, c->d_label, w, c->obj_p[1], c->d_grad_base, c->d_hess_base);
   } else {
     return fail("lgbcu_get_gradients: no objective set");
   }

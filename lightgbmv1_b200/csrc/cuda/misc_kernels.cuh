@@ -37,6 +37,30 @@ __global__ void k_grad_l2(int n, const double* __restrict__ score, const float* 
   }
 }
 
+// MulticlassSoftmax::GetGradients (src/objective/multiclass_objective.hpp:86-130): one thread per row over the K score
+// planes (class-major, [k][n]); Common::Softmax's order of operations (max, exp(x - max) summed in class order, divide)
+__global__ void k_grad_multiclass(int n, int K, const double* __restrict__ score, const float* __restrict__ label,
+                                  const float* __restrict__ weight, double factor, float* __restrict__ grad, float* __restrict__ hess) {
+  for (int i = blockIdx.x * blockDim.x + threadIdx.x; i < n; i += gridDim.x * blockDim.x) {
+    double wmax = score[i];
+    for (int k = 1; k < K; ++k) wmax = fmax(score[(size_t)n * k + i], wmax);
+    double wsum = 0.0;
+    for (int k = 0; k < K; ++k) wsum += exp(score[(size_t)n * k + i] - wmax);
+    const int lab = (int)label[i];
+    for (int k = 0; k < K; ++k) {
+      const size_t idx = (size_t)n * k + i;
+      const double p = exp(score[idx] - wmax) / wsum;
+      if (weight == nullptr) {
+        grad[idx] = lab == k ? (float)(p - 1.0f) : (float)p;
+        hess[idx] = (float)(factor * p * (1.0f - p));
+      } else {
+        grad[idx] = lab == k ? (float)((p - 1.0f) * weight[i]) : (float)(p * weight[i]);
+        hess[idx] = (float)((factor * p * (1.0f - p)) * weight[i]);
+      }
+    }
+  }
+}
+
 // max |g|, max |h| as float bit patterns (non-negative floats order like unsigned ints)
 // Also writes the interleaved (g, h) copy the histogram kernel gathers from: one 8-byte load per indexed row
 // instead of two 4-byte loads in two different sectors.

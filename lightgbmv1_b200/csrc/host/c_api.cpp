@@ -204,22 +204,22 @@ int LGBM_BoosterGetCurrentIteration(BoosterHandle handle, int* out_iteration) {
 
 int LGBM_BoosterNumModelPerIteration(BoosterHandle handle, int* out_tree_per_iteration) {
   API_BEGIN();
-  (void)handle;
-  *out_tree_per_iteration = 1;
+  Booster* b = reinterpret_cast<Booster*>(handle);
+  *out_tree_per_iteration = b->loaded ? 1 : b->gbdt->num_tree_per_iteration();
   API_END();
 }
 
 int LGBM_BoosterNumberOfTotalModel(BoosterHandle handle, int* out_models) {
   API_BEGIN();
   Booster* b = reinterpret_cast<Booster*>(handle);
-  *out_models = b->loaded ? static_cast<int>(b->loaded->trees.size()) : b->gbdt->current_iteration();
+  *out_models = b->loaded ? static_cast<int>(b->loaded->trees.size()) : b->gbdt->num_models();
   API_END();
 }
 
 int LGBM_BoosterGetNumClasses(BoosterHandle handle, int* out_len) {
   API_BEGIN();
-  (void)handle;
-  *out_len = 1;
+  Booster* b = reinterpret_cast<Booster*>(handle);
+  *out_len = b->loaded ? 1 : b->gbdt->num_tree_per_iteration();
   API_END();
 }
 
@@ -227,7 +227,7 @@ int LGBM_BoosterGetNumPredict(BoosterHandle handle, int data_idx, int64_t* out_l
   API_BEGIN();
   GBDT* g = reinterpret_cast<Booster*>(handle)->gbdt.get();
   if (data_idx < 0 || data_idx > g->num_valid()) Log::Fatal("Check failed: data_idx >= 0 && data_idx <= number of validation sets");
-  *out_len = data_idx == 0 ? g->num_data() : g->valid_num_data(data_idx - 1);
+  *out_len = static_cast<int64_t>(data_idx == 0 ? g->num_data() : g->valid_num_data(data_idx - 1)) * g->num_tree_per_iteration();
   API_END();
 }
 
@@ -238,10 +238,10 @@ int LGBM_BoosterGetPredict(BoosterHandle handle, int data_idx, int64_t* out_len,
   if (data_idx < 0 || data_idx > b->gbdt->num_valid()) Log::Fatal("Check failed: data_idx >= 0 && data_idx <= number of validation sets");
   if (data_idx == 0) {
     b->gbdt->GetTrainScore(out_result, true);
-    *out_len = b->gbdt->num_data();
+    *out_len = static_cast<int64_t>(b->gbdt->num_data()) * b->gbdt->num_tree_per_iteration();
   } else {
     b->gbdt->GetValidScore(data_idx - 1, out_result, true);
-    *out_len = b->gbdt->valid_num_data(data_idx - 1);
+    *out_len = static_cast<int64_t>(b->gbdt->valid_num_data(data_idx - 1)) * b->gbdt->num_tree_per_iteration();
   }
   API_END();
 }
@@ -327,7 +327,7 @@ int LGBM_BoosterPredictForMat(BoosterHandle handle, const void* data, int data_t
   }
   b->gbdt->PredictMat(data, data_type, nrow, ncol, is_row_major != 0, predict_type == C_API_PREDICT_RAW_SCORE,
                       num_iteration, out_result);
-  *out_len = nrow;
+  *out_len = static_cast<int64_t>(nrow) * b->gbdt->num_tree_per_iteration();
   API_END();
 }
 
@@ -512,10 +512,11 @@ int LGBM_BoosterFeatureImportance(BoosterHandle handle, int num_iteration, int i
 int LGBM_BoosterCalcNumPredict(BoosterHandle handle, int num_row, int predict_type, int start_iteration, int num_iteration,
                                int64_t* out_len) {
   API_BEGIN();
-  (void)handle; (void)start_iteration; (void)num_iteration;
+  (void)start_iteration; (void)num_iteration;
   if (predict_type != C_API_PREDICT_NORMAL && predict_type != C_API_PREDICT_RAW_SCORE)
     Log::Fatal("predict_type %d is outside this library's path (normal, raw score)", predict_type);
-  *out_len = num_row;   // one class, one value per row
+  Booster* b = reinterpret_cast<Booster*>(handle);
+  *out_len = static_cast<int64_t>(num_row) * (b->loaded ? 1 : b->gbdt->num_tree_per_iteration());   // one value per row and class
   API_END();
 }
 

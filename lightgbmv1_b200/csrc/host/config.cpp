@@ -109,6 +109,7 @@ std::string ObjectiveAlias(std::string t) {
   if (t == "regression" || t == "regression_l2" || t == "mean_squared_error" || t == "mse" || t == "l2" ||
       t == "l2_root" || t == "root_mean_squared_error" || t == "rmse") return "regression";
   if (t == "none" || t == "null" || t == "custom" || t == "na") return "custom";
+  if (t == "multiclass" || t == "softmax") return "multiclass";
   return t;
 }
 
@@ -261,7 +262,14 @@ void Config::Set(const std::unordered_map<std::string, std::string>& p) {
   if (lambda_l1 < 0 || lambda_l2 < 0) Log::Fatal("lambda_l1 / lambda_l2 should be >= 0");
   if (min_gain_to_split < 0) Log::Fatal("min_gain_to_split should be >= 0");
   if (bin_construct_sample_cnt <= 0) Log::Fatal("bin_construct_sample_cnt should be > 0");
-  if (num_class != 1) Log::Fatal("num_class=%d: multiclass is outside this library's path", num_class);
+  // CheckParamConflict (src/io/config.cpp:249-273): objective, metric and num_class must agree
+  if (objective == "multiclass") {
+    if (num_class <= 1) Log::Fatal("Number of classes should be specified and greater than 1 for multiclass training");
+  } else {
+    if (num_class != 1) Log::Fatal("Number of classes must be 1 for non-multiclass training");
+  }
+  GetInt(p, "multi_error_top_k", &multi_error_top_k);
+  if (multi_error_top_k <= 0) Log::Fatal("multi_error_top_k should be > 0");
   // CheckParamConflict (src/io/config.cpp:275-287): one machine => serial learner
   if (num_machines <= 1) tree_learner = "serial";
   if (max_depth > 0) {  // config.cpp:309-320: cap num_leaves by the depth

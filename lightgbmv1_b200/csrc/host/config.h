@@ -25,6 +25,7 @@ struct Config {
   int gpu_device_id = -1;
   int verbosity = 1;
   int num_class = 1;
+  int multi_error_top_k = 1;
   // tree
   int max_depth = -1;
   int min_data_in_leaf = 20;

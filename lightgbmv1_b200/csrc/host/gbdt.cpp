@@ -47,6 +47,9 @@ GBDT::GBDT(const Dataset* train, const Config& config)
   int dev = config_.gpu_device_id >= 0 ? config_.gpu_device_id : 0;
   if (Net().active && config_.gpu_device_id < 0 && ndev > 0) dev = Net().rank % ndev;
   Check(lgbcu_create(dev, &ctx_));
+  num_tree_per_iteration_ = objective_ ? objective_->NumModelPerIteration() : 1;
+  Check(lgbcu_set_num_class(ctx_, num_tree_per_iteration_));   // before the dataset: the score / gradient planes
+  class_need_train_.assign(num_tree_per_iteration_, 1);
   st.tick("lgbcu_create");
   // the communicator comes first: the objective's Init sums class counts over the machines
   data_parallel_ = Net().active && Net().num_machines > 1 && config_.tree_learner == "data";
@@ -54,7 +57,7 @@ GBDT::GBDT(const Dataset* train, const Config& config)
   if (objective_) {
     LgbCuContext* ctx = ctx_;
     objective_->Init(train_->metadata(), N, [ctx](double* v, int n) { Check(lgbcu_comm_allreduce_sum_f64(ctx, v, n)); });
-    class_need_train_ = objective_->NeedTrain();
+    for (int k = 0; k < num_tree_per_iteration_; ++k) class_need_train_[k] = objective_->NeedTrain(k) ? 1 : 0;
   }
   st.tick("comm + objective init");
   std::vector<LgbCuFeatureMeta> meta(F);
@@ -90,7 +93,15 @@ GBDT::GBDT(const Dataset* train, const Config& config)
   if (!md.query_boundaries.empty())
     Check(lgbcu_set_query(ctx_, md.query_boundaries.data(), static_cast<int>(md.query_boundaries.size()) - 1));
   if (objective_) objective_->Configure(ctx_);
-  if (!md.init_score.empty()) { Check(lgbcu_set_score(ctx_, md.init_score.data(), N)); has_init_score_ = true; }
+  if (!md.init_score.empty()) {   // [class][row] like the reference's ScoreUpdater
+    if (md.init_score.size() != static_cast<size_t>(N) * num_tree_per_iteration_) Log::Fatal("Initial score size doesn't match data size");
+    for (int k = 0; k < num_tree_per_iteration_; ++k) {
+      Check(lgbcu_set_class(ctx_, k));
+      Check(lgbcu_set_score(ctx_, md.init_score.data() + static_cast<size_t>(k) * N, N));
+    }
+    Check(lgbcu_set_class(ctx_, 0));
+    has_init_score_ = true;
+  }
   records_.resize(std::max(config_.num_leaves - 1, 1));
   st.tick("labels/objective/comm");
   // ---- metrics (Metric::CreateMetric, src/metric/metric.cpp:16-63; "custom" yields none)
@@ -107,14 +118,22 @@ GBDT::GBDT(const Dataset* train, const Config& config)
       spec.kind = LGBCU_METRIC_NDCG;
       for (int k : eval_at_) spec.names.push_back("ndcg@" + std::to_string(k));
     }
+    else if (m == "multi_logloss") { spec.kind = LGBCU_METRIC_MULTI_LOGLOSS; spec.names = {"multi_logloss"}; }
+    else if (m == "multi_error") {
+      spec.kind = LGBCU_METRIC_MULTI_ERROR;
+      spec.names = {config_.multi_error_top_k == 1 ? std::string("multi_error") : "multi_error@" + std::to_string(config_.multi_error_top_k)};
+    }
     else if (m == "custom") continue;
-    else Log::Fatal("metric=%s is outside this library's path (l2, rmse, binary_logloss, auc, ndcg)", m.c_str());
+    else Log::Fatal("metric=%s is outside this library's path (l2, rmse, binary_logloss, auc, ndcg, multi_logloss, multi_error)", m.c_str());
+    if ((spec.kind == LGBCU_METRIC_MULTI_LOGLOSS || spec.kind == LGBCU_METRIC_MULTI_ERROR) != (num_tree_per_iteration_ > 1))
+      Log::Fatal("Multiclass objective and metrics don't match");
     metrics_.push_back(spec);
   }
 
   // ---- GOSS::ResetGoss (goss.hpp:77-101)
   is_goss_ = config_.boosting == "goss";
   if (is_goss_) {
+    if (num_tree_per_iteration_ > 1) Log::Fatal("boosting=goss with a multiclass objective is outside this library's path");
     if (!(config_.top_rate + config_.other_rate <= 1.0)) Log::Fatal("Check failed: config_->top_rate + config_->other_rate <= 1.0f");
     if (!(config_.top_rate > 0.0 && config_.other_rate > 0.0)) Log::Fatal("Check failed: config_->top_rate > 0.0f && config_->other_rate > 0.0f");
     if (config_.bagging_freq > 0 && config_.bagging_fraction != 1.0) Log::Fatal("Cannot use bagging in GOSS");
@@ -248,79 +267,91 @@ void GBDT::GossSample(int iter) {
 
 bool GBDT::TrainOneIter(const float* grad, const float* hess) {
   const int N = train_->num_data();
-  double init_score = 0.0;
+  const int K = num_tree_per_iteration_;
+  std::vector<double> init_scores(K, 0.0);
   StageTimer st;
   if (grad == nullptr || hess == nullptr) {
     if (!objective_) Log::Fatal("No object function provided");
-    // BoostFromAverage (gbdt.cpp:312-335)
+    // BoostFromAverage (gbdt.cpp:312-335), once per class
     if (models_.empty() && !has_init_score_ && config_.boost_from_average) {
-      double s = objective_->BoostFromScore();
-      if (data_parallel_) {  // Network::GlobalSyncUpByMean
-        Check(lgbcu_comm_allreduce_sum_f64(ctx_, &s, 1));
-        s /= Net().num_machines;
-      }
-      if (std::fabs(s) > kEpsilon) {
-        init_score = s;
-        Check(lgbcu_add_score_const(ctx_, init_score));
-        for (const ValidEntry& v : valid_) Check(lgbcu_valid_add_const(ctx_, v.set, init_score));
-        Log::Info("Start training from score %lf", init_score);
+      for (int k = 0; k < K; ++k) {
+        double s = objective_->BoostFromScore(k);
+        if (data_parallel_) {  // Network::GlobalSyncUpByMean
+          Check(lgbcu_comm_allreduce_sum_f64(ctx_, &s, 1));
+          s /= Net().num_machines;
+        }
+        if (std::fabs(s) > kEpsilon) {
+          init_scores[k] = s;
+          Check(lgbcu_set_class(ctx_, k));
+          Check(lgbcu_add_score_const(ctx_, s));
+          for (const ValidEntry& v : valid_) Check(lgbcu_valid_add_const(ctx_, v.set, s));
+          Log::Info("Start training from score %lf", s);
+        }
       }
     }
     st.tick("boost from average");
-    Check(lgbcu_get_gradients(ctx_));  // GBDT::Boosting
+    Check(lgbcu_get_gradients(ctx_));  // GBDT::Boosting: every class's gradients from the scores as they are now
   } else {
-    Check(lgbcu_set_gradients(ctx_, grad, hess, N));
+    for (int k = 0; k < K; ++k) {
+      Check(lgbcu_set_class(ctx_, k));
+      Check(lgbcu_set_gradients(ctx_, grad + static_cast<size_t>(k) * N, hess + static_cast<size_t>(k) * N, N));
+    }
   }
-  Bagging(iter_);
+  Check(lgbcu_set_class(ctx_, 0));
+  Bagging(iter_);   // one bag per iteration, shared by the iteration's trees
 
-  std::unique_ptr<Tree> tree(new Tree(2));
   bool should_continue = false;
   const bool bagged = (use_bagging_ || is_goss_) && bag_cnt_ < N;
-  if (class_need_train_) {
-    ResetFeatureMask();  // BeforeTrain: col_sampler_.ResetByTree()
-    Check(lgbcu_begin_tree(ctx_, bagged ? LGBCU_DEVICE_BAG : nullptr, bagged ? bag_cnt_ : 0,
-                           need_reset_bytree_ ? feature_used_.data() : nullptr));
-    int ns = 0;
-    st.tick("gradients/bagging/begin_tree");
-    Check(lgbcu_train_tree(ctx_, records_.data(), &ns));
-    st.tick("lgbcu_train_tree");
-    tree.reset(new Tree(config_.num_leaves));
-    for (int i = 0; i < ns; ++i) {
-      const LgbCuSplitRecord& r = records_[i];
-      const BinMapper& m = train_->mapper(r.feature);
-      tree->Split(r.leaf, r.feature, r.real_feature, static_cast<uint32_t>(r.threshold), m.BinToValue(r.threshold),
-                  r.left_output, r.right_output, r.left_count, r.right_count, r.left_sum_hessian, r.right_sum_hessian,
-                  r.gain, m.missing_type(), r.default_left != 0);
+  for (int k = 0; k < K; ++k) {   // GBDT::TrainOneIter's loop over cur_tree_id (gbdt.cpp:353-412)
+    Check(lgbcu_set_class(ctx_, k));
+    std::unique_ptr<Tree> tree(new Tree(2));
+    if (class_need_train_[k]) {
+      ResetFeatureMask();  // BeforeTrain: col_sampler_.ResetByTree()
+      Check(lgbcu_begin_tree(ctx_, bagged ? LGBCU_DEVICE_BAG : nullptr, bagged ? bag_cnt_ : 0,
+                             need_reset_bytree_ ? feature_used_.data() : nullptr));
+      int ns = 0;
+      st.tick("gradients/bagging/begin_tree");
+      Check(lgbcu_train_tree(ctx_, records_.data(), &ns));
+      st.tick("lgbcu_train_tree");
+      tree.reset(new Tree(config_.num_leaves));
+      for (int i = 0; i < ns; ++i) {
+        const LgbCuSplitRecord& r = records_[i];
+        const BinMapper& m = train_->mapper(r.feature);
+        tree->Split(r.leaf, r.feature, r.real_feature, static_cast<uint32_t>(r.threshold), m.BinToValue(r.threshold),
+                    r.left_output, r.right_output, r.left_count, r.right_count, r.left_sum_hessian, r.right_sum_hessian,
+                    r.gain, m.missing_type(), r.default_left != 0);
+      }
     }
+    if (tree->num_leaves() > 1) {
+      should_continue = true;
+      tree->Shrinkage(shrinkage_rate_);
+      // UpdateScore (gbdt.cpp:458-478): in-bag rows through the partition, out-of-bag rows by walking the tree
+      Check(lgbcu_add_score_by_partition(ctx_, tree->leaf_values().data(), tree->num_leaves()));
+      if (bagged) {
+        std::vector<int> thr(tree->threshold_in_bin().begin(), tree->threshold_in_bin().end());
+        Check(lgbcu_add_score_by_tree(ctx_, tree->num_leaves(), tree->split_feature_inner().data(), thr.data(),
+                                      tree->decision_type().data(), tree->left_child().data(), tree->right_child().data(),
+                                      tree->leaf_values().data(), LGBCU_DEVICE_OOB, N - bag_cnt_, 0));
+      }
+      AddTreeToValid(*tree);
+      if (std::fabs(init_scores[k]) > kEpsilon) tree->AddBias(init_scores[k]);
+    } else {
+      if (models_.size() < static_cast<size_t>(K)) {  // only add default score one-time (gbdt.cpp:385-401)
+        double output = 0.0;
+        if (!class_need_train_[k]) { if (objective_) output = objective_->BoostFromScore(k); }
+        else output = init_scores[k];
+        tree->AsConstantTree(output);
+        Check(lgbcu_add_score_const(ctx_, output));
+        for (const ValidEntry& v : valid_) Check(lgbcu_valid_add_const(ctx_, v.set, output));
+      }
+    }
+    st.tick("tree + score update");
+    models_.push_back(std::move(tree));
   }
-  if (tree->num_leaves() > 1) {
-    should_continue = true;
-    tree->Shrinkage(shrinkage_rate_);
-    // UpdateScore (gbdt.cpp:458-478): in-bag rows through the partition, out-of-bag rows by walking the tree
-    Check(lgbcu_add_score_by_partition(ctx_, tree->leaf_values().data(), tree->num_leaves()));
-    if (bagged) {
-      std::vector<int> thr(tree->threshold_in_bin().begin(), tree->threshold_in_bin().end());
-      Check(lgbcu_add_score_by_tree(ctx_, tree->num_leaves(), tree->split_feature_inner().data(), thr.data(),
-                                    tree->decision_type().data(), tree->left_child().data(), tree->right_child().data(),
-                                    tree->leaf_values().data(), LGBCU_DEVICE_OOB, N - bag_cnt_, 0));
-    }
-    AddTreeToValid(*tree);
-    if (std::fabs(init_score) > kEpsilon) tree->AddBias(init_score);
-  } else {
-    if (models_.empty()) {  // only add default score one-time (gbdt.cpp:385-401)
-      double output = 0.0;
-      if (!class_need_train_) { if (objective_) output = objective_->BoostFromScore(); }
-      else output = init_score;
-      tree->AsConstantTree(output);
-      Check(lgbcu_add_score_const(ctx_, output));
-      for (const ValidEntry& v : valid_) Check(lgbcu_valid_add_const(ctx_, v.set, output));
-    }
-  }
-  st.tick("tree + score update");
-  models_.push_back(std::move(tree));
+  Check(lgbcu_set_class(ctx_, 0));
   if (!should_continue) {
     Log::Warning("Stopped training because there are no more leaves that meet the split requirements");
-    if (models_.size() > 1) models_.pop_back();
+    if (models_.size() > static_cast<size_t>(K)) for (int k = 0; k < K; ++k) models_.pop_back();
     return true;
   }
   ++iter_;
@@ -330,12 +361,14 @@ bool GBDT::TrainOneIter(const float* grad, const float* hess) {
 void GBDT::GetTrainScore(double* out, bool converted) const {
   const int N = train_->num_data();
   StageTimer st;
-  Check(lgbcu_copy_score(ctx_, out, N));
-  st.tick("copy scores to host");
-  if (converted && objective_) {
-#pragma omp parallel for schedule(static)
-    for (int i = 0; i < N; ++i) { double v = out[i]; objective_->ConvertOutput(&v, &out[i]); }
+  const int K = num_tree_per_iteration_;
+  for (int k = 0; k < K; ++k) {   // [class][row], the reference's GetPredictAt layout before conversion
+    Check(lgbcu_set_class(ctx_, k));
+    Check(lgbcu_copy_score(ctx_, out + static_cast<size_t>(k) * N, N));
   }
+  Check(lgbcu_set_class(ctx_, 0));
+  st.tick("copy scores to host");
+  if (converted && objective_) ConvertScores(out, N);
   st.tick("convert output");
 }
 
@@ -367,15 +400,25 @@ void GBDT::AddValidData(const Dataset* valid) {
   if (!md.weights.empty()) Check(lgbcu_valid_set_weight(ctx_, e.set, md.weights.data(), n));
   if (!md.query_boundaries.empty())
     Check(lgbcu_valid_set_query(ctx_, e.set, md.query_boundaries.data(), static_cast<int>(md.query_boundaries.size()) - 1));
-  if (!md.init_score.empty()) Check(lgbcu_valid_set_score(ctx_, e.set, md.init_score.data(), n));  // ScoreUpdater ctor
+  if (!md.init_score.empty()) {  // ScoreUpdater ctor
+    if (md.init_score.size() != static_cast<size_t>(n) * num_tree_per_iteration_) Log::Fatal("Initial score size doesn't match data size");
+    for (int k = 0; k < num_tree_per_iteration_; ++k) {
+      Check(lgbcu_set_class(ctx_, k));
+      Check(lgbcu_valid_set_score(ctx_, e.set, md.init_score.data() + static_cast<size_t>(k) * n, n));
+    }
+    Check(lgbcu_set_class(ctx_, 0));
+  }
   valid_.push_back(e);
-  // the trees grown so far
-  for (const auto& t : models_) {
+  // the trees grown so far (tree i belongs to class i % K)
+  for (size_t i = 0; i < models_.size(); ++i) {
+    const auto& t = models_[i];
     std::vector<int> thr(t->threshold_in_bin().begin(), t->threshold_in_bin().end());
+    Check(lgbcu_set_class(ctx_, static_cast<int>(i % num_tree_per_iteration_)));
     Check(lgbcu_valid_add_tree(ctx_, e.set, t->num_leaves(), t->split_feature_inner().data(), thr.data(),
                                t->decision_type().data(), t->left_child().data(), t->right_child().data(),
                                t->leaf_values().data()));
   }
+  Check(lgbcu_set_class(ctx_, 0));
   for (const MetricSpec& m : metrics_) {
     if (m.kind == LGBCU_METRIC_NDCG) SetupNdcg(e.set, md, n);
     if (md.label.empty()) Log::Fatal("Label should not be NULL");
@@ -458,7 +501,9 @@ std::vector<double> GBDT::GetEvalAt(int data_idx) {
     }
     double buf[64];
     // metrics convert the raw score through the objective (ObjectiveFunction::ConvertOutput): a sigmoid for binary
-    const double sig = (objective_ && std::string(objective_->Name()) == "binary") ? config_.sigmoid : 0.0;
+    double sig = (objective_ && std::string(objective_->Name()) == "binary") ? config_.sigmoid : 0.0;
+    if (m.kind == LGBCU_METRIC_MULTI_LOGLOSS) sig = objective_ ? 1.0 : 0.0;                                       // softmax first
+    if (m.kind == LGBCU_METRIC_MULTI_ERROR) sig = (objective_ ? 1.0 : -1.0) * config_.multi_error_top_k;
     Check(lgbcu_eval(ctx_, set, m.kind, sig, buf, 64));
     for (size_t i = 0; i < m.names.size(); ++i) ret.push_back(buf[i]);
   }
@@ -467,10 +512,31 @@ std::vector<double> GBDT::GetEvalAt(int data_idx) {
 
 void GBDT::GetValidScore(int idx, double* out, bool converted) const {
   const int N = valid_[idx].data->num_data();
-  Check(lgbcu_valid_copy_score(ctx_, valid_[idx].set, out, N));
-  if (converted && objective_) {
+  for (int k = 0; k < num_tree_per_iteration_; ++k) {
+    Check(lgbcu_set_class(ctx_, k));
+    Check(lgbcu_valid_copy_score(ctx_, valid_[idx].set, out + static_cast<size_t>(k) * N, N));
+  }
+  Check(lgbcu_set_class(ctx_, 0));
+  if (converted && objective_) ConvertScores(out, N);
+}
+
+// ObjectiveFunction::ConvertOutput over [class][row] planes (GBDT::GetPredictAt, gbdt.cpp:612-624)
+void GBDT::ConvertScores(double* out, int N) const {
+  const int K = num_tree_per_iteration_;
+  if (K == 1) {
 #pragma omp parallel for schedule(static)
     for (int i = 0; i < N; ++i) { double v = out[i]; objective_->ConvertOutput(&v, &out[i]); }
+    return;
+  }
+#pragma omp parallel
+  {
+    std::vector<double> raw(K), conv(K);
+#pragma omp for schedule(static)
+    for (int i = 0; i < N; ++i) {
+      for (int k = 0; k < K; ++k) raw[k] = out[static_cast<size_t>(k) * N + i];
+      objective_->ConvertOutput(raw.data(), conv.data());
+      for (int k = 0; k < K; ++k) out[static_cast<size_t>(k) * N + i] = conv[k];
+    }
   }
 }
 
@@ -478,34 +544,41 @@ void GBDT::PredictMat(const void* data, int data_type, int32_t nrow, int32_t nco
                       int num_iteration, double* out) const {
   if (ncol != train_->num_total_features())
     Log::Fatal("The number of features in data (%d) is not the same as it was in training data (%d).", ncol, train_->num_total_features());
-  int n_models = static_cast<int>(models_.size());
-  if (num_iteration > 0) n_models = std::min(n_models, num_iteration);
+  const int K = num_tree_per_iteration_;
+  int n_iter = static_cast<int>(models_.size()) / K;
+  if (num_iteration > 0) n_iter = std::min(n_iter, num_iteration);
 #pragma omp parallel
   {
-    std::vector<double> row(ncol);
+    std::vector<double> row(ncol), s(K), conv(K);
 #pragma omp for schedule(static)
     for (int32_t r = 0; r < nrow; ++r) {
       for (int c = 0; c < ncol; ++c) {
         const size_t i = row_major ? static_cast<size_t>(r) * ncol + c : static_cast<size_t>(c) * nrow + r;
         row[c] = data_type == 0 ? static_cast<double>(static_cast<const float*>(data)[i]) : static_cast<const double*>(data)[i];
       }
-      double s = 0.0;
-      for (int m = 0; m < n_models; ++m) s += models_[m]->Predict(row.data());
-      if (!raw_score && objective_) objective_->ConvertOutput(&s, &s);
-      out[r] = s;
+      // GBDT::PredictRaw (gbdt_prediction.cpp:13-31): tree i * K + k adds to class k; a row's K outputs are adjacent
+      for (int k = 0; k < K; ++k) s[k] = 0.0;
+      for (int it = 0; it < n_iter; ++it) for (int k = 0; k < K; ++k) s[k] += models_[static_cast<size_t>(it) * K + k]->Predict(row.data());
+      if (!raw_score && objective_) { objective_->ConvertOutput(s.data(), conv.data()); for (int k = 0; k < K; ++k) s[k] = conv[k]; }
+      for (int k = 0; k < K; ++k) out[static_cast<size_t>(r) * K + k] = s[k];
     }
   }
 }
 
 void GBDT::RollbackOneIter() {
-  if (models_.empty()) return;
-  Tree& t = *models_.back();
-  t.ScaleLeafValues(-1.0);   // Tree::Shrinkage(-1): subtracting the tree = adding its negative
-  std::vector<int> thr(t.threshold_in_bin().begin(), t.threshold_in_bin().end());
-  Check(lgbcu_add_score_by_tree(ctx_, t.num_leaves(), t.split_feature_inner().data(), thr.data(), t.decision_type().data(),
-                                t.left_child().data(), t.right_child().data(), t.leaf_values().data(), nullptr, 0, 0));
-  AddTreeToValid(t);
-  models_.pop_back();
+  const int K = num_tree_per_iteration_;
+  if (iter_ <= 0 || models_.size() < static_cast<size_t>(K)) return;
+  for (int k = 0; k < K; ++k) {
+    Tree& t = *models_[models_.size() - K + k];
+    t.ScaleLeafValues(-1.0);   // Tree::Shrinkage(-1): subtracting the tree = adding its negative
+    std::vector<int> thr(t.threshold_in_bin().begin(), t.threshold_in_bin().end());
+    Check(lgbcu_set_class(ctx_, k));
+    Check(lgbcu_add_score_by_tree(ctx_, t.num_leaves(), t.split_feature_inner().data(), thr.data(), t.decision_type().data(),
+                                  t.left_child().data(), t.right_child().data(), t.leaf_values().data(), nullptr, 0, 0));
+    AddTreeToValid(t);
+  }
+  Check(lgbcu_set_class(ctx_, 0));
+  for (int k = 0; k < K; ++k) models_.pop_back();
   --iter_;
 }
 
@@ -527,7 +600,7 @@ void GBDT::ResetParameter(const Config& merged) {
 std::vector<double> GBDT::FeatureImportance(int num_iteration, int importance_type) const {
   std::vector<double> imp(train_->num_total_features(), 0.0);
   int n_models = static_cast<int>(models_.size());
-  if (num_iteration > 0) n_models = std::min(n_models, num_iteration);
+  if (num_iteration > 0) n_models = std::min(n_models, num_iteration * num_tree_per_iteration_);
   for (int m = 0; m < n_models; ++m) {
     const Tree& t = *models_[m];
     for (int i = 0; i < t.num_leaves() - 1; ++i) {
@@ -540,7 +613,7 @@ std::vector<double> GBDT::FeatureImportance(int num_iteration, int importance_ty
 std::vector<double> GBDT::FeatureImportanceSplit(int num_iteration) const {
   std::vector<double> imp(train_->num_total_features(), 0.0);
   int n_models = static_cast<int>(models_.size());
-  if (num_iteration > 0) n_models = std::min(n_models, num_iteration);
+  if (num_iteration > 0) n_models = std::min(n_models, num_iteration * num_tree_per_iteration_);
   for (int m = 0; m < n_models; ++m) {
     const Tree& t = *models_[m];
     for (int i = 0; i < t.num_leaves() - 1; ++i) if (t.split_gain()[i] > 0) imp[t.split_feature()[i]] += 1.0;
@@ -553,8 +626,8 @@ std::string GBDT::SaveModelToString(int start_iteration, int num_iteration) cons
   std::ostringstream ss;
   ss << "tree" << '\n';
   ss << "version=v3" << '\n';
-  ss << "num_class=1" << '\n';
-  ss << "num_tree_per_iteration=1" << '\n';
+  ss << "num_class=" << num_tree_per_iteration_ << '\n';
+  ss << "num_tree_per_iteration=" << num_tree_per_iteration_ << '\n';
   ss << "label_index=0" << '\n';
   ss << "max_feature_idx=" << train_->num_total_features() - 1 << '\n';
   if (objective_) ss << "objective=" << objective_->ToString() << '\n';
@@ -566,14 +639,15 @@ std::string GBDT::SaveModelToString(int start_iteration, int num_iteration) cons
     for (size_t i = 0; i < fi.size(); ++i) { if (i) infos += ' '; infos += fi[i]; }
     ss << "feature_infos=" << infos << '\n';
   }
-  int num_used = static_cast<int>(models_.size());
-  const int total_iter = num_used;
+  int num_used = static_cast<int>(models_.size());   // gbdt_model_text.cpp:336-347: iterations -> models
+  const int total_iter = num_used / num_tree_per_iteration_;
   start_iteration = std::min(std::max(start_iteration, 0), total_iter);
-  if (num_iteration > 0) num_used = std::min(start_iteration + num_iteration, num_used);
+  if (num_iteration > 0) num_used = std::min((start_iteration + num_iteration) * num_tree_per_iteration_, num_used);
+  const int start_model = start_iteration * num_tree_per_iteration_;
   std::vector<std::string> strs;
   std::string sizes;
-  for (int i = start_iteration; i < num_used; ++i) {
-    strs.push_back("Tree=" + std::to_string(i - start_iteration) + '\n' + models_[i]->ToString() + '\n');
+  for (int i = start_model; i < num_used; ++i) {
+    strs.push_back("Tree=" + std::to_string(i - start_model) + '\n' + models_[i]->ToString() + '\n');
     if (!sizes.empty()) sizes += ' ';
     sizes += std::to_string(strs.back().size());
   }

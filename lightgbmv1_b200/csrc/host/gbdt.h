@@ -29,7 +29,9 @@ class GBDT {
   GBDT(const Dataset* train, const Config& config);
   ~GBDT();
   bool TrainOneIter(const float* grad, const float* hess);  // true = finished (cannot split any more)
-  int current_iteration() const { return static_cast<int>(models_.size()); }
+  int current_iteration() const { return static_cast<int>(models_.size()) / num_tree_per_iteration_; }   // GBDT::GetCurrentIteration
+  int num_models() const { return static_cast<int>(models_.size()); }
+  int num_tree_per_iteration() const { return num_tree_per_iteration_; }
   int num_data() const { return train_->num_data(); }
   void GetTrainScore(double* out, bool converted) const;      // LGBM_BoosterGetPredict(data_idx = 0)
   // validation data and metrics (GBDT::AddValidDataset / GetEvalAt, src/boosting/gbdt.cpp:121-149, 545-565; the metric
@@ -65,6 +67,7 @@ class GBDT {
   std::vector<ValidEntry> valid_;
   bool train_ndcg_ready_ = false;
   void Bagging(int iter);
+  void ConvertScores(double* out, int N) const;
   void ResetFeatureMask();
   std::vector<double> FeatureImportanceSplit(int num_iteration) const;
 
@@ -77,7 +80,8 @@ class GBDT {
   double shrinkage_rate_;
   bool has_init_score_ = false;
   bool data_parallel_ = false;  // this booster trains over the NCCL communicator (tree_learner=data, num_machines > 1)
-  bool class_need_train_ = true;
+  int num_tree_per_iteration_ = 1;            // = num_class for multiclass (one tree and one score plane per class)
+  std::vector<char> class_need_train_;        // ObjectiveFunction::ClassNeedTrain per class
   // bagging (gbdt.cpp:209-243, 739-797)
   data_size_t bag_cnt_;     // the bag itself (in-bag rows ascending, then out-of-bag rows) lives on the device
   bool use_bagging_ = false;

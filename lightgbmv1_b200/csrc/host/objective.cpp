@@ -42,7 +42,7 @@ class BinaryLogloss : public Objective {
   void Configure(LgbCuContext* ctx) const override {
     Check(lgbcu_set_objective(ctx, LGBCU_OBJ_BINARY, sigmoid_, label_weights_[0], label_weights_[1]));
   }
-  double BoostFromScore() const override {
+  double BoostFromScore(int) const override {
     double suml = 0.0f, sumw = 0.0f;
     if (weights_) {  // (the reference reduces over OpenMP threads too: binary_objective.hpp BoostFromScore)
 #pragma omp parallel for schedule(static) reduction(+:suml, sumw)
@@ -58,7 +58,7 @@ class BinaryLogloss : public Objective {
     Log::Info("[binary:BoostFromScore]: pavg=%f -> initscore=%f", pavg, init);
     return init;
   }
-  bool NeedTrain() const override { return need_train_; }
+  bool NeedTrain(int) const override { return need_train_; }
   void ConvertOutput(const double* in, double* out) const override { out[0] = 1.0f / (1.0f + std::exp(-sigmoid_ * in[0])); }
   std::string ToString() const override { std::ostringstream o; o << "binary sigmoid:" << sigmoid_; return o.str(); }
   const char* Name() const override { return "binary"; }
@@ -80,7 +80,7 @@ class RegressionL2 : public Objective {
     if (meta.label.empty()) Log::Fatal("Label should not be NULL");
   }
   void Configure(LgbCuContext* ctx) const override { Check(lgbcu_set_objective(ctx, LGBCU_OBJ_L2, 0, 0, 0)); }
-  double BoostFromScore() const override {
+  double BoostFromScore(int) const override {
     double suml = 0.0f, sumw = 0.0f;
     if (weights_) {  // (OpenMP reductions as in regression_objective.hpp BoostFromScore)
 #pragma omp parallel for schedule(static) reduction(+:suml, sumw)
@@ -114,7 +114,7 @@ class Lambdarank : public Objective {
     Check(lgbcu_set_objective(ctx, LGBCU_OBJ_LAMBDARANK, sigmoid_, trunc_, norm_ ? 1 : 0));
     if (!label_gain_.empty()) Check(lgbcu_set_label_gain(ctx, label_gain_.data(), static_cast<int>(label_gain_.size())));
   }
-  double BoostFromScore() const override { return 0.0; }
+  double BoostFromScore(int) const override { return 0.0; }
   std::string ToString() const override { return "lambdarank"; }
   const char* Name() const override { return "lambdarank"; }
 
@@ -124,12 +124,68 @@ class Lambdarank : public Objective {
 
 }  // namespace
 
+// src/objective/multiclass_objective.hpp (MulticlassSoftmax)
+class MulticlassSoftmax : public Objective {
+ public:
+  explicit MulticlassSoftmax(const Config& c) : num_class_(c.num_class) {
+    factor_ = static_cast<double>(num_class_) / (num_class_ - 1.0f);
+  }
+  void Init(const Metadata& meta, data_size_t n, const SumSync& sum_over_ranks) override {
+    num_data_ = n;
+    if (meta.label.empty()) Log::Fatal("Label should not be NULL");
+    const label_t* label = meta.label.data();
+    const label_t* weights = meta.weights.empty() ? nullptr : meta.weights.data();
+    class_init_probs_.assign(num_class_, 0.0);
+    double sum_weight = 0.0;
+    for (data_size_t i = 0; i < n; ++i) {   // sequential like the reference: the order of the double sums is part of the result
+      const int li = static_cast<int>(label[i]);
+      if (li < 0 || li >= num_class_) Log::Fatal("Label must be in [0, %d), but found %d in label", num_class_, li);
+      if (weights == nullptr) class_init_probs_[li] += 1.0;
+      else { class_init_probs_[li] += weights[i]; sum_weight += weights[i]; }
+    }
+    if (weights == nullptr) sum_weight = n;
+    {  // Network::GlobalSyncUpBySum of the total and of every class
+      std::vector<double> v(class_init_probs_);
+      v.push_back(sum_weight);
+      sum_over_ranks(v.data(), static_cast<int>(v.size()));
+      sum_weight = v.back();
+      for (int k = 0; k < num_class_; ++k) class_init_probs_[k] = v[k];
+    }
+    for (int k = 0; k < num_class_; ++k) class_init_probs_[k] /= sum_weight;
+  }
+  void Configure(LgbCuContext* ctx) const override {
+    Check(lgbcu_set_objective(ctx, LGBCU_OBJ_MULTICLASS, num_class_, factor_, 0));
+  }
+  double BoostFromScore(int class_id) const override {
+    return std::log(std::max<double>(kEpsilon, class_init_probs_[class_id]));
+  }
+  bool NeedTrain(int class_id) const override {
+    const double p = std::fabs(class_init_probs_[class_id]);
+    return !(p <= kEpsilon || p >= 1.0 - kEpsilon);
+  }
+  int NumModelPerIteration() const override { return num_class_; }
+  void ConvertOutput(const double* in, double* out) const override {  // Common::Softmax
+    double wmax = in[0];
+    for (int i = 1; i < num_class_; ++i) wmax = std::max(in[i], wmax);
+    double wsum = 0.0f;
+    for (int i = 0; i < num_class_; ++i) { out[i] = std::exp(in[i] - wmax); wsum += out[i]; }
+    for (int i = 0; i < num_class_; ++i) out[i] /= static_cast<double>(wsum);
+  }
+  std::string ToString() const override { std::ostringstream o; o << "multiclass num_class:" << num_class_; return o.str(); }
+  const char* Name() const override { return "multiclass"; }
+
+ private:
+  int num_class_; double factor_; data_size_t num_data_ = 0;
+  std::vector<double> class_init_probs_;
+};
+
 Objective* Objective::Create(const Config& c) {
+  if (c.objective == "multiclass") return new MulticlassSoftmax(c);
   if (c.objective == "binary") return new BinaryLogloss(c);
   if (c.objective == "regression") return new RegressionL2(c);
   if (c.objective == "lambdarank") return new Lambdarank(c);
   if (c.objective == "custom") return nullptr;
-  Log::Fatal("objective=%s is outside this library's path (binary, regression/l2, lambdarank, custom)", c.objective.c_str());
+  Log::Fatal("objective=%s is outside this library's path (binary, regression/l2, lambdarank, multiclass, custom)", c.objective.c_str());
 }
 
 }  // namespace lgb

@@ -22,8 +22,10 @@ class Objective {
   typedef std::function<void(double*, int)> SumSync;
   virtual void Init(const Metadata& meta, data_size_t num_data, const SumSync& sum_over_ranks) = 0;
   virtual void Configure(LgbCuContext* ctx) const = 0;  // push kind + parameters to the device learner
-  virtual double BoostFromScore() const = 0;
-  virtual bool NeedTrain() const { return true; }
+  virtual double BoostFromScore(int class_id = 0) const = 0;
+  virtual bool NeedTrain(int class_id = 0) const { return true; }   // ObjectiveFunction::ClassNeedTrain
+  virtual int NumModelPerIteration() const { return 1; }           // trees (= score planes) per boosting iteration
+  // ConvertOutput works on one row's NumModelPerIteration() raw scores
   virtual data_size_t NumPositiveData() const { return 0; }  // rows of this machine with label > 0 (balanced bagging)
   virtual bool IsConstantHessian() const { return false; }
   virtual void ConvertOutput(const double* in, double* out) const { out[0] = in[0]; }

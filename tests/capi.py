@@ -96,14 +96,15 @@ class LGBMLib:
         self.check(self.lib.LGBM_BoosterGetEval(b, C.c_int(data_idx), C.byref(ln), out.ctypes.data_as(C.POINTER(C.c_double))))
         return out[:ln.value]
 
-    def predict_mat(self, b, X, raw=False, num_iteration=-1):
+    def predict_mat(self, b, X, raw=False, num_iteration=-1, num_class=1):
         X = np.ascontiguousarray(X)
-        out = np.empty(X.shape[0], dtype=np.float64)
+        out = np.empty(X.shape[0] * num_class, dtype=np.float64)
         ln = C.c_int64(0)
         self.check(self.lib.LGBM_BoosterPredictForMat(
             b, X.ctypes.data_as(C.c_void_p), C.c_int(DTYPE_F32 if X.dtype == np.float32 else DTYPE_F64),
             C.c_int32(X.shape[0]), C.c_int32(X.shape[1]), C.c_int(1), C.c_int(1 if raw else 0), C.c_int(0),
             C.c_int(num_iteration), C.c_char_p(b""), C.byref(ln), out.ctypes.data_as(C.POINTER(C.c_double))))
+        assert ln.value == out.size
         return out
 
     def model_string(self, b):
