@@ -33,6 +33,8 @@ struct LoadedModel {
   int max_feature_idx = -1;
   std::string objective;   // the header's objective line, e.g. "binary sigmoid:1"
   double sigmoid = 0.0;    // > 0: predictions are 1 / (1 + exp(-sigmoid * raw))
+  int num_tree_per_iteration = 1;   // multiclass: trees (and outputs per row) per iteration
+  bool softmax = false;             // "multiclass ...": predictions are the softmax of a row's raw scores
 };
 
 struct Booster {
@@ -69,8 +71,10 @@ LoadedModel* ParseModel(const std::string& text) {
     if (k == "max_feature_idx") m->max_feature_idx = std::atoi(v.c_str());
     else if (k == "objective") m->objective = v;
     else if (k == "feature_names") m->feature_names = SplitAny(v, " ");
-    else if (k == "num_class" && std::atoi(v.c_str()) != 1) Log::Fatal("multiclass models are outside this library's path");
+    else if (k == "num_tree_per_iteration") m->num_tree_per_iteration = std::max(1, std::atoi(v.c_str()));
   }
+  if (m->objective.rfind("multiclassova", 0) == 0) Log::Fatal("multiclassova models are outside this library's path");
+  m->softmax = m->objective.rfind("multiclass", 0) == 0;
   if (m->max_feature_idx < 0) Log::Fatal("Model file doesn't specify max_feature_idx");
   if (m->objective.rfind("binary", 0) == 0) {
     m->sigmoid = 1.0;
@@ -198,14 +202,14 @@ int LGBM_BoosterUpdateOneIterCustom(BoosterHandle handle, const float* grad, con
 int LGBM_BoosterGetCurrentIteration(BoosterHandle handle, int* out_iteration) {
   API_BEGIN();
   Booster* b = reinterpret_cast<Booster*>(handle);
-  *out_iteration = b->loaded ? static_cast<int>(b->loaded->trees.size()) : b->gbdt->current_iteration();
+  *out_iteration = b->loaded ? static_cast<int>(b->loaded->trees.size()) / b->loaded->num_tree_per_iteration : b->gbdt->current_iteration();
   API_END();
 }
 
 int LGBM_BoosterNumModelPerIteration(BoosterHandle handle, int* out_tree_per_iteration) {
   API_BEGIN();
   Booster* b = reinterpret_cast<Booster*>(handle);
-  *out_tree_per_iteration = b->loaded ? 1 : b->gbdt->num_tree_per_iteration();
+  *out_tree_per_iteration = b->loaded ? b->loaded->num_tree_per_iteration : b->gbdt->num_tree_per_iteration();
   API_END();
 }
 
@@ -219,7 +223,7 @@ int LGBM_BoosterNumberOfTotalModel(BoosterHandle handle, int* out_models) {
 int LGBM_BoosterGetNumClasses(BoosterHandle handle, int* out_len) {
   API_BEGIN();
   Booster* b = reinterpret_cast<Booster*>(handle);
-  *out_len = b->loaded ? 1 : b->gbdt->num_tree_per_iteration();
+  *out_len = b->loaded ? b->loaded->num_tree_per_iteration : b->gbdt->num_tree_per_iteration();
   API_END();
 }
 
@@ -304,25 +308,33 @@ int LGBM_BoosterPredictForMat(BoosterHandle handle, const void* data, int data_t
     const LoadedModel& m = *b->loaded;
     if (ncol != m.max_feature_idx + 1)
       Log::Fatal("The number of features in data (%d) is not the same as it was in training data (%d).", ncol, m.max_feature_idx + 1);
-    int n_models = static_cast<int>(m.trees.size());
-    if (num_iteration > 0) n_models = std::min(n_models, num_iteration);
+    const int K = m.num_tree_per_iteration;
+    int n_iter = static_cast<int>(m.trees.size()) / K;
+    if (num_iteration > 0) n_iter = std::min(n_iter, num_iteration);
     const bool raw = predict_type == C_API_PREDICT_RAW_SCORE;
 #pragma omp parallel
     {
-      std::vector<double> row(ncol);
+      std::vector<double> row(ncol), sc(K);
 #pragma omp for schedule(static)
       for (int32_t r = 0; r < nrow; ++r) {
         for (int c = 0; c < ncol; ++c) {
           const size_t i = is_row_major ? static_cast<size_t>(r) * ncol + c : static_cast<size_t>(c) * nrow + r;
           row[c] = data_type == 0 ? static_cast<double>(static_cast<const float*>(data)[i]) : static_cast<const double*>(data)[i];
         }
-        double sc = 0.0;
-        for (int t = 0; t < n_models; ++t) sc += m.trees[t]->Predict(row.data());
-        if (!raw && m.sigmoid > 0) sc = 1.0f / (1.0f + std::exp(-m.sigmoid * sc));
-        out_result[r] = sc;
+        for (int k = 0; k < K; ++k) sc[k] = 0.0;
+        for (int t = 0; t < n_iter; ++t) for (int k = 0; k < K; ++k) sc[k] += m.trees[static_cast<size_t>(t) * K + k]->Predict(row.data());
+        if (!raw && m.sigmoid > 0) sc[0] = 1.0f / (1.0f + std::exp(-m.sigmoid * sc[0]));
+        if (!raw && m.softmax) {   // Common::Softmax
+          double wmax = sc[0];
+          for (int k = 1; k < K; ++k) wmax = std::max(sc[k], wmax);
+          double wsum = 0.0f;
+          for (int k = 0; k < K; ++k) { sc[k] = std::exp(sc[k] - wmax); wsum += sc[k]; }
+          for (int k = 0; k < K; ++k) sc[k] /= static_cast<double>(wsum);
+        }
+        for (int k = 0; k < K; ++k) out_result[static_cast<size_t>(r) * K + k] = sc[k];
       }
     }
-    *out_len = nrow;
+    *out_len = static_cast<int64_t>(nrow) * K;
     return 0;
   }
   b->gbdt->PredictMat(data, data_type, nrow, ncol, is_row_major != 0, predict_type == C_API_PREDICT_RAW_SCORE,
@@ -516,7 +528,7 @@ int LGBM_BoosterCalcNumPredict(BoosterHandle handle, int num_row, int predict_ty
   if (predict_type != C_API_PREDICT_NORMAL && predict_type != C_API_PREDICT_RAW_SCORE)
     Log::Fatal("predict_type %d is outside this library's path (normal, raw score)", predict_type);
   Booster* b = reinterpret_cast<Booster*>(handle);
-  *out_len = static_cast<int64_t>(num_row) * (b->loaded ? 1 : b->gbdt->num_tree_per_iteration());   // one value per row and class
+  *out_len = static_cast<int64_t>(num_row) * (b->loaded ? b->loaded->num_tree_per_iteration : b->gbdt->num_tree_per_iteration());   // one value per row and class
   API_END();
 }
 

@@ -112,3 +112,23 @@ def test_lgb_train_through_the_reference_python_package():
     np.testing.assert_allclose(io_, ir, rtol=1e-6)
     for k in ("binary_logloss", "auc"):
         np.testing.assert_allclose(eo["v"][k], er["v"][k], rtol=1e-9)
+
+
+def test_loaded_multiclass_model_predicts_like_the_reference_cpu():
+    """a multiclass model the REFERENCE trained, loaded here from its text: K trees per iteration, softmax outputs"""
+    if not H.have_ref():
+        pytest.skip("oracle/_ref not built")
+    rng = np.random.default_rng(5)
+    X = rng.standard_normal((3000, 6))
+    y = (np.argmax(X[:, :3] + 0.5 * rng.standard_normal((3000, 3)), axis=1)).astype(np.float32)
+    ref, ours = capi.reference(), capi.ours()
+    _, br, _ = capi.train(ref, X, y, "objective=multiclass num_class=3 num_leaves=7 verbosity=-1 num_threads=2", 5)
+    text = ref.model_string(br)
+    bo = ours.load_model_from_string(text)
+    for raw in (True, False):
+        np.testing.assert_allclose(ours.predict_mat(bo, X, raw=raw, num_class=3), ref.predict_mat(br, X, raw=raw, num_class=3),
+                                   rtol=0, atol=1e-15)
+    k = C.c_int(0)
+    ours.check(ours.lib.LGBM_BoosterGetNumClasses(bo, C.byref(k))); assert k.value == 3
+    ours.check(ours.lib.LGBM_BoosterGetCurrentIteration(bo, C.byref(k))); assert k.value == 5
+    assert ours.model_string(bo) == text
