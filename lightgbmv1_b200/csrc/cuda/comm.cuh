@@ -9,6 +9,14 @@
 // SplitInfo all-reduce moves the same bytes in two steps).  NCCL is resolved with dlopen so that a single-GPU
 // process needs no NCCL at all, and so that a host process that already loaded an NCCL (torch) shares it.
 //
+// Two ranks (one-shot exchange): no collective on the histograms at all.  k_hist adds into a second pool that is
+// exported with CUDA IPC; one launch per round (k_xchg_pull, split_kernels.cuh) publishes the round with a flag in the
+// peer's memory, waits for the peer's flag (bounded: a peer that never arrives voids the tree, it does not hang the
+// GPU), and sums the ranks' local slots -- the peer's read over NVLink with plain system-scope loads -- into the pool
+// the split search reads.  Sized on the device: only the live items' slots travel, which the host-enqueued NCCL call
+// cannot know.  Measured: 3.18 vs 3.34 ms per iteration at 2 ranks, 3.12 vs 2.87 at 8 (every rank pulls 7 x the
+// slots), hence two ranks only by default.
+//
 // Wide data (ownership mode, the reference's own scheme): each rank owns a contiguous block of features (balanced by
 // bins).  Per round: a grouped ncclReduce per (fresh slot, owner) leaves every owner with the global histogram of its
 // block (the reference's ReduceScatter, data_parallel_tree_learner.cpp:176-186), the split search scans only the

@@ -66,6 +66,7 @@ struct DevLeaf {     // DataPartition range + LeafSplits + pool slot of one leaf
 // then commits, in the reference's order, every leaf whose turn has come and whose children are ready.  An expansion
 // is only wasted if the leaf budget runs out before the leaf's turn.
 #define LGB_KMAX 16
+#define LGB_MAX_PEERS 8   /* ranks of a one-shot exchange (one NVLink box) */
 
 struct DevSpec {     // an expanded leaf that is not committed yet: what Split + two FindBestThreshold runs produced
   DevLeaf child[2];  // [0] = left (keeps the parent's leaf id when committed), [1] = right (gets the next free id)
@@ -103,6 +104,9 @@ struct DevCtl {
   // what k_hist builds in the current round, written by k_partition (part_expand): per item the rows of the smaller
   // child (0 = nothing to build) and the child itself -- one dependent load for k_hist's preamble instead of the
   // item_leaf -> spec -> child chain
+  unsigned long long xchg_epoch;  // one-shot exchange: rounds this rank has published (monotonic over the booster's life)
+  int xchg_error;                 // a peer's flag did not arrive in time: the tree is void (checked by the host)
+  unsigned xchg_done;             // "last block" counter of k_xchg_pull
   int hist_rows[LGB_KMAX];
   DevLeaf hist_leaf[LGB_KMAX];
   // what k_partition splits in the current round, written by the control step of k_find_split after its commits:
@@ -127,6 +131,12 @@ struct DevView {
   int data_parallel;         // 1: histograms are all-reduced across ranks, leaf counts are the global estimates
   int f_begin, f_end;        // features this rank scans in k_find_split: all of them, or its block in ownership mode
   int comm_size;             // ranks (ownership mode: rows of cand_all per (leaf, child))
+  // One-shot exchange (data-parallel, comm.cuh): k_hist adds into pool_local; k_xchg_pull publishes the round, waits
+  // for the peers and sums the ranks' local slots over NVLink into `pool`; no NCCL collective on the histogram.
+  int xchg, comm_rank;
+  HistEntry* pool_local;                      // this rank's local sums, slot for slot like `pool`
+  const HistEntry* xpool[LGB_MAX_PEERS];      // rank r's pool_local as mapped here (own entry = pool_local)
+  unsigned long long* xflags;                 // [comm_size] epoch rank r has published up to (written by rank r)
   CandRec* cand_send;        // [2 * LGB_KMAX]              ownership mode: this rank's winners of the round
   CandRec* cand_all;         // [comm_size][2 * LGB_KMAX]   every rank's, after the all-gather
   const uint8_t* bins;

@@ -532,6 +532,69 @@ struct FindTarget {
   const int8_t* parent_split;   // the expanded leaf's is_splittable flags (nullptr: none)
 };
 
+// ---- one-shot exchange (data-parallel; comm.cuh) -----------------------------------------------------------------
+// k_hist has added this rank's rows into pool_local.  One launch then does what the NCCL all-reduce did, sized on the
+// device (only the slots of the round's live items, which the host cannot know):
+//   * publish: block 0 writes this rank's next epoch into every peer's flag array (the launch follows this rank's
+//     k_hist in stream order; a system-scope fence orders the histogram adds before the flag);
+//   * wait: every block polls its OWN flag array until every rank has reached that epoch -- all ranks run the same
+//     live rounds, so the epochs agree.  The wait is bounded: a peer that never arrives voids the tree (xchg_error)
+//     instead of hanging the GPU;
+//   * pull + reduce: entry by entry, pool[slot] = sum over the ranks' pool_local[slot], the peers' read over NVLink
+//     with system-scope loads.  64-bit integers: exact, the same on every rank.
+// The last block to finish records the epoch.  The split search afterwards reads `pool` exactly as it does on one GPU.
+#define XCHG_TIMEOUT_CYCLES 6000000000ll   /* ~3 s */
+#define XCHG_THREADS 256
+struct XchgPeers { unsigned long long* flags[LGB_MAX_PEERS]; };   // rank r's flag array as mapped here
+__global__ void __launch_bounds__(XCHG_THREADS) k_xchg_pull(DevView V, XchgPeers P) {
+  DevCtl* c = V.ctl;
+  if (c->done) return;
+  const bool root_round = c->round == 0;
+  if (root_round && c->skip_find) return;
+  const unsigned long long need = c->xchg_epoch + 1;
+  __shared__ int s_last;
+  if (threadIdx.x == 0) {
+    if (blockIdx.x == 0) {
+      __threadfence_system();
+      for (int r = 0; r < V.comm_size; ++r)
+        if (r != V.comm_rank) *reinterpret_cast<volatile unsigned long long*>(P.flags[r] + V.comm_rank) = need;
+    }
+    const long long t0 = clock64();
+    for (int r = 0; r < V.comm_size; ++r) {
+      if (r == V.comm_rank) continue;
+      const volatile unsigned long long* fl = V.xflags + r;
+      while (*fl < need) {
+        if (clock64() - t0 > XCHG_TIMEOUT_CYCLES) { c->xchg_error = 1; break; }
+      }
+    }
+    __threadfence_system();
+  }
+  __syncthreads();
+  const int ni = root_round ? 1 : c->num_items;
+  const long long per = V.total_bin;
+  const long long total = per * ni;
+  for (long long e = (long long)blockIdx.x * XCHG_THREADS + threadIdx.x; e < total; e += (long long)gridDim.x * XCHG_THREADS) {
+    const int i = (int)(e / per);
+    const size_t slot = root_round ? 0 : (size_t)(1 + (c->round - 1) * c->lookahead + i);
+    const size_t idx = slot * (size_t)V.total_bin + (size_t)(e - (long long)i * per);
+    i64 g = 0, h = 0;
+    for (int r = 0; r < V.comm_size; ++r) {
+      // (volatile: the peers' memory must not be served from a stale L1 line)
+      const volatile i64* p = reinterpret_cast<const volatile i64*>(V.xpool[r] + idx);
+      g += p[0]; h += p[1];
+    }
+    HistEntry o; o.g = g; o.h = h;
+    V.pool[idx] = o;
+  }
+  __syncthreads();
+  if (threadIdx.x == 0) {
+    __threadfence();
+    const unsigned ticket = atomicAdd(&c->xchg_done, 1u);
+    s_last = ticket == gridDim.x - 1;
+    if (s_last) { c->xchg_done = 0; c->xchg_epoch = need; }
+  }
+}
+
 __device__ void find_item(const DevView& V, ScanSmem& S, int f, int sel, const FindTarget& T) {
   DevCtl* c = V.ctl;
   const int tid = threadIdx.x;
@@ -549,6 +612,7 @@ __device__ void find_item(const DevView& V, ScanSmem& S, int f, int sel, const F
     const int nt = F.num_bin - F.offset;
     const double inv_g = c->inv_g, inv_h = c->inv_h;
     HistEntry* hs = V.pool + (size_t)Ls.slot * V.total_bin + F.hist_base;  // smaller leaf, slot 0 of the group
+
     double2* fix_s = V.mfb_fix + (size_t)Ls.slot * V.num_features + f;
     DevSplit o; int sp = 0;
     o.gain = LGB_MIN_SCORE; o.feature = -1; o.real_feature = -1;
