@@ -202,7 +202,7 @@ struct LgbCuContext {
   // data-parallel
   ncclComm_t comm = nullptr; int rank = 0, world = 1;
   // one-shot exchange (comm.cuh): the ranks read each other's local histograms over NVLink; LGBCU_DP_ONESHOT
-  bool xchg = false; int xchg_cfg = -1; bool xchg_tried = false;
+  bool xchg = false; int xchg_cfg = -1; bool xchg_tried = false; bool xchg_two_step = false;   // LGBCU_DP_ONESHOT=2: the two-step form
   HistEntry* d_pool_local = nullptr; size_t pool_local_entries = 0;       // plain cudaMalloc: exported with CUDA IPC
   unsigned long long* d_xflags = nullptr;
   void* xpeer_pool[LGB_MAX_PEERS] = {nullptr}; void* xpeer_flags[LGB_MAX_PEERS] = {nullptr};   // peers' mappings
@@ -638,7 +638,7 @@ int lgbcu_create(int device_id, LgbCuContext** out) {
   c->num_sms = sm_count;
   if (const char* e = std::getenv("LGBCU_HIST_MIN_ROWS")) { const int v = std::atoi(e); if (v >= 1) c->hist_min_rows = v; }
   if (const char* e = std::getenv("LGBCU_DP_OWNERSHIP")) c->dp_owner_cfg = std::atoi(e) != 0 ? 1 : 0;
-  if (const char* e = std::getenv("LGBCU_DP_ONESHOT")) c->xchg_cfg = std::atoi(e) != 0 ? 1 : 0;
+  if (const char* e = std::getenv("LGBCU_DP_ONESHOT")) { const int v = std::atoi(e); c->xchg_cfg = v != 0 ? 1 : 0; c->xchg_two_step = v == 2; }
   if (const char* e = std::getenv("LGBCU_HIST_SMALL_ROWS")) { const int v = std::atoi(e); if (v >= 0) c->hist_small_rows = v; }
   CU(cudaStreamCreateWithFlags(&c->stream, cudaStreamNonBlocking));
   CU(dev_alloc(&c->d_ctl, 1));
@@ -1278,7 +1278,12 @@ static int enqueue_round(LgbCuContext* c, int round, cudaEvent_t* ev) {
     if (c->xchg) {
       XchgPeers P;
       for (int r = 0; r < LGB_MAX_PEERS; ++r) P.flags[r] = r == c->rank ? c->d_xflags : static_cast<unsigned long long*>(c->xpeer_flags[r]);
-      LAUNCH(k_xchg_pull, c->num_sms * 2, XCHG_THREADS, 0, c->stream, V, P);
+      if (c->xchg_two_step) {
+        LAUNCH(k_xchg_pull, c->num_sms * 2, XCHG_THREADS, 0, c->stream, V, P, 1);
+        LAUNCH(k_xchg_pull, c->num_sms * 2, XCHG_THREADS, 0, c->stream, V, P, 2);
+      } else {
+        LAUNCH(k_xchg_pull, c->num_sms * 2, XCHG_THREADS, 0, c->stream, V, P, 0);
+      }
     } else if (comm_reduce_hist(c, first, count, round == 0)) return -1;
   }
   if (round == 0) LAUNCH(k_root_sums, 1, 32, 0, c->stream, V);

@@ -546,13 +546,9 @@ struct FindTarget {
 #define XCHG_TIMEOUT_CYCLES 6000000000ll   /* ~3 s */
 #define XCHG_THREADS 256
 struct XchgPeers { unsigned long long* flags[LGB_MAX_PEERS]; };   // rank r's flag array as mapped here
-__global__ void __launch_bounds__(XCHG_THREADS) k_xchg_pull(DevView V, XchgPeers P) {
+// publish this rank's epoch `need` (block 0) and wait until every rank has reached it (every block)
+__device__ __forceinline__ void xchg_publish_and_wait(const DevView& V, const XchgPeers& P, unsigned long long need) {
   DevCtl* c = V.ctl;
-  if (c->done) return;
-  const bool root_round = c->round == 0;
-  if (root_round && c->skip_find) return;
-  const unsigned long long need = c->xchg_epoch + 1;
-  __shared__ int s_last;
   if (threadIdx.x == 0) {
     if (blockIdx.x == 0) {
       __threadfence_system();
@@ -570,29 +566,57 @@ __global__ void __launch_bounds__(XCHG_THREADS) k_xchg_pull(DevView V, XchgPeers
     __threadfence_system();
   }
   __syncthreads();
+}
+__device__ __forceinline__ void xchg_finish(const DevView& V, unsigned long long need) {
+  DevCtl* c = V.ctl;
+  __syncthreads();
+  if (threadIdx.x == 0) {
+    __threadfence_system();   // (step 1 of the two-step form: the reduced slice must be out before the next flag)
+    const unsigned ticket = atomicAdd(&c->xchg_done, 1u);
+    if (ticket == gridDim.x - 1) { c->xchg_done = 0; c->xchg_epoch = need; }
+  }
+}
+// step: 0 = the one-step form (two ranks): every entry of the live slots = sum over the ranks' local slots;
+//       1 = two-step form, first half: this rank reduces ITS 1/N slice of every live slot over all ranks, in place in
+//           its pool_local (nobody else reads that slice of this rank's pool_local) and into pool;
+//       2 = second half: the other slices are copied from their owners' pool_local.  (N - 1) / N of a slot is read per
+//           half instead of N - 1 slots in the one-step form.
+__global__ void __launch_bounds__(XCHG_THREADS) k_xchg_pull(DevView V, XchgPeers P, int step) {
+  DevCtl* c = V.ctl;
+  if (c->done) return;
+  const bool root_round = c->round == 0;
+  if (root_round && c->skip_find) return;
+  const unsigned long long need = c->xchg_epoch + 1;
+  xchg_publish_and_wait(V, P, need);
   const int ni = root_round ? 1 : c->num_items;
   const long long per = V.total_bin;
+  const int N = V.comm_size, me = V.comm_rank;
+  const long long sl = (per + N - 1) / N;   // entries per slice
   const long long total = per * ni;
   for (long long e = (long long)blockIdx.x * XCHG_THREADS + threadIdx.x; e < total; e += (long long)gridDim.x * XCHG_THREADS) {
     const int i = (int)(e / per);
+    const long long off = e - (long long)i * per;
+    const int owner = (int)(off / sl);
+    if (step == 1 && owner != me) continue;
+    if (step == 2 && owner == me) continue;
     const size_t slot = root_round ? 0 : (size_t)(1 + (c->round - 1) * c->lookahead + i);
-    const size_t idx = slot * (size_t)V.total_bin + (size_t)(e - (long long)i * per);
+    const size_t idx = slot * (size_t)V.total_bin + (size_t)off;
     i64 g = 0, h = 0;
-    for (int r = 0; r < V.comm_size; ++r) {
+    if (step == 2) {
       // (volatile: the peers' memory must not be served from a stale L1 line)
-      const volatile i64* p = reinterpret_cast<const volatile i64*>(V.xpool[r] + idx);
-      g += p[0]; h += p[1];
+      const volatile i64* p = reinterpret_cast<const volatile i64*>(V.xpool[owner] + idx);
+      g = p[0]; h = p[1];
+    } else {
+      for (int r = 0; r < N; ++r) {
+        const volatile i64* p = reinterpret_cast<const volatile i64*>(V.xpool[r] + idx);
+        g += p[0]; h += p[1];
+      }
     }
     HistEntry o; o.g = g; o.h = h;
     V.pool[idx] = o;
+    if (step == 1) V.pool_local[idx] = o;
   }
-  __syncthreads();
-  if (threadIdx.x == 0) {
-    __threadfence();
-    const unsigned ticket = atomicAdd(&c->xchg_done, 1u);
-    s_last = ticket == gridDim.x - 1;
-    if (s_last) { c->xchg_done = 0; c->xchg_epoch = need; }
-  }
+  xchg_finish(V, need);
 }
 
 __device__ void find_item(const DevView& V, ScanSmem& S, int f, int sel, const FindTarget& T) {

@@ -83,8 +83,9 @@ def test_two_rank_feature_ownership_mode(tmp_path, sorted_shards):
 
 
 @pytest.mark.gpu
+@pytest.mark.parametrize("form", ["0", "1", "2"])   # NCCL all-reduce / one-step pull (the 2-rank default) / two-step (slice reduce + gather)
 @pytest.mark.parametrize("sorted_shards", [False, True])
-def test_two_rank_one_shot_exchange(tmp_path, sorted_shards):
+def test_two_rank_one_shot_exchange(tmp_path, sorted_shards, form):
     """No collective on the histograms: every rank adds into a local pool exported with CUDA IPC, publishes each round
     with a flag in its peers' memory, and the split search sums the ranks' local slots over NVLink while it loads them
     (LGBCU_DP_ONESHOT=1).  Integer sums: the model must equal the NCCL all-reduce mode's bit for bit -- the reference's
@@ -94,7 +95,7 @@ def test_two_rank_one_shot_exchange(tmp_path, sorted_shards):
     one, two = str(tmp_path / "one.txt"), str(tmp_path / "two.txt")
     cmd = [sys.executable, SCRIPT, "--out", one] + (["--sorted-shards"] if sorted_shards else [])
     subprocess.check_call(cmd, env=dict(os.environ, LGBCU_FORCE_DP_COUNTS="1"), timeout=600)
-    _torchrun(2, 29515 + int(sorted_shards), two, sorted_shards=sorted_shards, env={"LGBCU_DP_ONESHOT": "1", "LGBCU_VERBOSE": "1"})
+    _torchrun(2, 29515 + int(sorted_shards) + 2 * int(form), two, sorted_shards=sorted_shards, env={"LGBCU_DP_ONESHOT": form})
     a, b = open(one).read(), open(two).read()
     if not sorted_shards:
         _assert_same(open(GOLDEN).read(), b, "reference 2-machine socket run vs 2-rank run with the one-shot exchange")
