@@ -37,6 +37,7 @@ __global__ void __launch_bounds__(RANK_THREADS) k_lambdarank(RankDev R, int max_
   double* s_score = reinterpret_cast<double*>(rsm);                       // [cnt] by rank
   int* s_label = reinterpret_cast<int*>(s_score + max_query);             // [cnt] by rank
   int* s_doc = s_label + max_query;                                       // [cnt] rank -> doc
+  int* s_own = s_doc + max_query;                                         // [cnt] thread position -> rank it owns
   __shared__ double s_red[RANK_THREADS / 32];
   __shared__ double s_sum;
   const int q = blockIdx.x;
@@ -63,16 +64,27 @@ __global__ void __launch_bounds__(RANK_THREADS) k_lambdarank(RankDev R, int max_
   if (worst_idx > 0 && s_score[worst_idx] == LGB_MIN_SCORE) worst_idx -= 1;
   const double worst_score = s_score[worst_idx];
   const bool use_norm_dist = R.norm && best_score != worst_score;
-  double local_sum = 0.0;
+  // Which document a thread owns: position t of the order (label, rank).  The lanes of a warp then mostly share a
+  // label, so "this pair contributes" (the other document's label is higher / lower than mine) is the same for the whole
+  // warp and the ~70 % of pairs that contribute nothing are skipped by a uniform branch.  Every document still receives
+  // its terms in the reference's order of i, so the float sums are bit for bit what they were.
   for (int r = threadIdx.x; r < cnt; r += blockDim.x) {
-    // this thread owns the document at rank r
-    const double my_score = s_score[r];
-    const int my_label = s_label[r];
-    const double my_gain = R.label_gain[my_label];
-    const double my_disc = R.discount[r];
+    const int L = s_label[r];
+    int pos = 0;
+    for (int e = 0; e < cnt; ++e) { const int le = s_label[e]; pos += (le < L) || (le == L && e < r); }
+    s_own[pos] = r;
+  }
+  __syncthreads();
+  double local_sum = 0.0;
+  const int cnt_pad = (cnt + 31) / 32 * 32;
+  for (int t = threadIdx.x; t < cnt_pad; t += blockDim.x) {
+    // this thread owns the document at rank r (lanes past the end of the query run the loops with nothing to add)
+    const int r = t < cnt ? s_own[t] : -1;
+    const double my_score = r >= 0 ? s_score[r] : LGB_MIN_SCORE;
+    const int my_label = r >= 0 ? s_label[r] : 0;
+    const double my_disc = r >= 0 ? R.discount[r] : 0.0;
     float lam = 0.0f, hes = 0.0f;
-    // One pair term.  Written without branches so that the table look-ups and divisions of neighbouring pairs overlap:
-    // a pair that the reference skips contributes exactly +0 (x - 0 == x and x + 0 == x bit for bit).
+    // One pair term.  A pair that the reference skips contributes exactly +0 (x - 0 == x and x + 0 == x bit for bit).
     auto pair_term = [&](double high_score, int high_label, double high_disc, double low_score, int low_label,
                          double low_disc, bool ok, double* pl, double* ph) {
       const double delta_score = ok ? high_score - low_score : 0.0;
@@ -87,38 +99,33 @@ __global__ void __launch_bounds__(RANK_THREADS) k_lambdarank(RankDev R, int max_
       *pl = ok ? p_lambda : 0.0;
       *ph = ok ? p_hessian : 0.0;
     };
-    const bool me_valid = my_score != LGB_MIN_SCORE;
-    // ranks before r: doc is the lower-labelled one of pair (i, r)
-#pragma unroll 4
-    for (int i = 0; i < r; ++i) {
-      const double hs = s_score[i]; const int hl = s_label[i];
+    const bool me_valid = r >= 0 && my_score != LGB_MIN_SCORE;
+    // doc as the higher-labelled one: the reference sums these in double over all j, in order, when its walk reaches
+    // rank r
+    double high_sum_lambda = 0.0, high_sum_hessian = 0.0;
+    for (int j = 0; j < cnt; ++j) {
+      const double ls = s_score[j]; const int ll = s_label[j];
+      const bool ok = me_valid && j != r && ls != LGB_MIN_SCORE && my_label > ll;
+      if (!__any_sync(0xffffffffu, ok)) continue;
       double pl, ph;
-      pair_term(hs, hl, R.discount[i], my_score, my_label, my_disc, me_valid && hs != LGB_MIN_SCORE && hl > my_label, &pl, &ph);
+      pair_term(my_score, my_label, my_disc, ls, ll, R.discount[j], ok, &pl, &ph);
+      high_sum_lambda += pl; high_sum_hessian += ph;
+      local_sum -= 2 * pl;
+    }
+    // the walk over i: for i != r the pair term where doc is the lower-labelled one; at i == r the sum above
+    for (int i = 0; i < cnt; ++i) {
+      if (i == r && me_valid) { lam += (float)high_sum_lambda; hes += (float)high_sum_hessian; }
+      const double hs = s_score[i]; const int hl = s_label[i];
+      const bool ok = me_valid && i != r && hs != LGB_MIN_SCORE && hl > my_label;
+      if (!__any_sync(0xffffffffu, ok)) continue;
+      double pl, ph;
+      pair_term(hs, hl, R.discount[i], my_score, my_label, my_disc, ok, &pl, &ph);
       lam -= (float)pl; hes += (float)ph;
     }
-    // rank r itself: doc is the higher-labelled one; the reference sums these in double over all j, in order
-    {
-      double high_sum_lambda = 0.0, high_sum_hessian = 0.0;
-#pragma unroll 4
-      for (int j = 0; j < cnt; ++j) {
-        const double ls = s_score[j]; const int ll = s_label[j];
-        double pl, ph;
-        pair_term(my_score, my_label, my_disc, ls, ll, R.discount[j], me_valid && j != r && ls != LGB_MIN_SCORE && my_label > ll, &pl, &ph);
-        high_sum_lambda += pl; high_sum_hessian += ph;
-        local_sum -= 2 * pl;
-      }
-      if (me_valid) { lam += (float)high_sum_lambda; hes += (float)high_sum_hessian; }
+    if (r >= 0) {
+      R.grad[start + s_doc[r]] = lam;
+      R.hess[start + s_doc[r]] = hes;
     }
-    // ranks after r
-#pragma unroll 4
-    for (int i = r + 1; i < cnt; ++i) {
-      const double hs = s_score[i]; const int hl = s_label[i];
-      double pl, ph;
-      pair_term(hs, hl, R.discount[i], my_score, my_label, my_disc, me_valid && hs != LGB_MIN_SCORE && hl > my_label, &pl, &ph);
-      lam -= (float)pl; hes += (float)ph;
-    }
-    R.grad[start + s_doc[r]] = lam;
-    R.hess[start + s_doc[r]] = hes;
   }
   // sum_lambdas over the block
   for (int o = 16; o > 0; o >>= 1) local_sum += __shfl_xor_sync(0xffffffffu, local_sum, o);
@@ -226,7 +233,7 @@ int rank_launch(LgbCuContext* c) {
   R.min_in = -50.0 / R.sigmoid / 2; R.max_in = -R.min_in;
   R.idx_factor = RANK_SIGMOID_BINS / (R.max_in - R.min_in);
   R.norm = c->rank_params.norm;
-  const size_t smem = (size_t)c->max_query * (sizeof(double) + 2 * sizeof(int));
+  const size_t smem = (size_t)c->max_query * (sizeof(double) + 3 * sizeof(int));
   NEED(smem <= 200 * 1024, "lambdarank: query of %d documents does not fit the per-query shared memory tile", c->max_query);
   if (!c->rank_attr_set) {  // the attribute is per device: kept per context, not per process
     CU(cudaFuncSetAttribute(k_lambdarank, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024));
