@@ -135,6 +135,8 @@ struct DevView {
   // for the peers and sums the ranks' local slots over NVLink into `pool`; no NCCL collective on the histogram.
   int xchg, comm_rank;
   HistEntry* pool_local;                      // this rank's local sums, slot for slot like `pool`
+  HistEntry* hist_pool;                       // where k_hist adds and k_partition zeroes: pool_local in that mode, else pool
+                                              // (one pointer, chosen on the host: a select in k_hist cost it a register spill)
   const HistEntry* xpool[LGB_MAX_PEERS];      // rank r's pool_local as mapped here (own entry = pool_local)
   unsigned long long* xflags;                 // [comm_size] epoch rank r has published up to (written by rank r)
   CandRec* cand_send;        // [2 * LGB_KMAX]              ownership mode: this rank's winners of the round

@@ -74,7 +74,7 @@ __device__ __forceinline__ i64 unpack_h(const int4& r) { return ((i64)(r.z >> 16
 
 __device__ void hist_global_path(const DevView& V, const DevLeaf& L, bool identity, int bid, int nblocks) {
   const int* idx = V.indices[L.buf] + L.begin;
-  HistEntry* out = (V.xchg ? V.pool_local : V.pool) + (size_t)L.slot * V.total_bin;
+  HistEntry* out = V.hist_pool + (size_t)L.slot * V.total_bin;
   const int nchunk = V.num_tiles16;
   const long long total = (long long)L.count * nchunk;
   for (long long p = bid * (long long)blockDim.x + threadIdx.x; p < total; p += (long long)nblocks * blockDim.x) {
@@ -151,7 +151,7 @@ __device__ void hist_shared_path(const DevView& V, const DevLeaf& L, bool identi
   int per_block = (L.count + PG * HIST_CLUSTER - 1) / (PG * HIST_CLUSTER);
   per_block = (per_block + 31) / 32 * 32;
   const int* idx = V.indices[L.buf] + L.begin;
-  HistEntry* out = (V.xchg ? V.pool_local : V.pool) + (size_t)L.slot * V.total_bin;
+  HistEntry* out = V.hist_pool + (size_t)L.slot * V.total_bin;
   const unsigned stride16 = (unsigned)V.row_stride / 16u;  // row offsets travel as 32-bit counts of 16 bytes (64 GB)
   const double sg = V.ctl->scale_g, sh = V.ctl->scale_h;
 #ifdef LGBCU_STAGE_TIMERS

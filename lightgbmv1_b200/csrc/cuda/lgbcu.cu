@@ -299,6 +299,7 @@ struct LgbCuContext {
     V.f_begin = 0; V.f_end = F; V.comm_size = world; V.cand_send = d_cand_send; V.cand_all = d_cand_all;
     if (dp_owner && (int)own_begin.size() == world + 1) { V.f_begin = own_begin[rank]; V.f_end = own_begin[rank + 1]; }
     V.xchg = (xchg && comm != nullptr) ? 1 : 0; V.comm_rank = rank; V.pool_local = d_pool_local; V.xflags = d_xflags;
+    V.hist_pool = V.xchg ? d_pool_local : d_pool;
     for (int r = 0; r < LGB_MAX_PEERS; ++r) V.xpool[r] = r == rank ? d_pool_local : static_cast<const HistEntry*>(xpeer_pool[r]);
     return V;
   }

@@ -147,7 +147,7 @@ __global__ void __launch_bounds__(PART_THREADS, PART_BLOCKS_PER_SM + 1) k_partit
     // the fresh histogram slots of this round's expansions (see part_expand) must be zero before k_hist adds to them:
     // every block of the grid clears a slice of each, whether or not it owns tiles
     for (int i = 0; i < ni; ++i) {
-      uint4* z = reinterpret_cast<uint4*>((V.xchg ? V.pool_local : V.pool) + (size_t)(1 + (c->round - 1) * c->lookahead + i) * V.total_bin);
+      uint4* z = reinterpret_cast<uint4*>(V.hist_pool + (size_t)(1 + (c->round - 1) * c->lookahead + i) * V.total_bin);
       const uint4 zero = make_uint4(0, 0, 0, 0);
       for (int k = blockIdx.x * PART_THREADS + threadIdx.x; k < V.total_bin; k += gridDim.x * PART_THREADS) z[k] = zero;
     }
