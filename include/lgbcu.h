@@ -43,7 +43,8 @@ typedef struct LgbCuContext LgbCuContext;
 /* missing_type values: include/LightGBM/bin.h (enum MissingType { None, Zero, NaN }) */
 enum { LGBCU_MISSING_NONE = 0, LGBCU_MISSING_ZERO = 1, LGBCU_MISSING_NAN = 2 };
 /* objective kinds implemented on device (src/objective/) */
-enum { LGBCU_OBJ_NONE = 0, LGBCU_OBJ_BINARY = 1, LGBCU_OBJ_L2 = 2, LGBCU_OBJ_LAMBDARANK = 3, LGBCU_OBJ_MULTICLASS = 4 };
+enum { LGBCU_OBJ_NONE = 0, LGBCU_OBJ_BINARY = 1, LGBCU_OBJ_L2 = 2, LGBCU_OBJ_LAMBDARANK = 3, LGBCU_OBJ_MULTICLASS = 4,
+       LGBCU_OBJ_L1 = 5, LGBCU_OBJ_QUANTILE = 6 };
 /* histogram kernel selection (LGBCU_HIST_AUTO picks by leaf size) */
 enum { LGBCU_HIST_AUTO = 0, LGBCU_HIST_GLOBAL_ATOMIC = 1, LGBCU_HIST_WARP_PRIVATE = 2 };
 
@@ -177,6 +178,14 @@ LGBCU_API int lgbcu_set_objective(LgbCuContext* ctx, int kind, double p0, double
  * validation-set calls -- works on, so one tree per class and iteration is grown exactly as a single-class tree is
  * (GBDT::TrainOneIter's loop over cur_tree_id, src/boosting/gbdt.cpp:353-412).  Set the number of classes before any
  * validation set is added. */
+/* l1 (regression_objective.hpp:214-231) and quantile (:491-516, p0 = alpha) have no second-order step worth keeping: after a
+ * tree is grown (and before its scores are added) lgbcu_renew_leaf_outputs recomputes every leaf's value as the
+ * (weighted) percentile of label - score over the rows the tree grew on -- SerialTreeLearner::RenewTreeOutput,
+ * serial_tree_learner.cpp:661-699, with PercentileFun / WeightedPercentileFun (regression_objective.hpp:18-88).
+ * alpha_is_float: the quantile objective holds alpha as a float and forms the position in float arithmetic.
+ * leaf_nonempty[l] = the leaf holds rows on this rank (data-parallel runs average over the ranks that do). */
+LGBCU_API int lgbcu_renew_leaf_outputs(LgbCuContext* ctx, int32_t num_leaves, double alpha, int32_t alpha_is_float,
+                                       double* leaf_values, int32_t* leaf_nonempty);
 LGBCU_API int lgbcu_set_num_class(LgbCuContext* ctx, int32_t num_class);
 LGBCU_API int lgbcu_set_class(LgbCuContext* ctx, int32_t class_id);
 LGBCU_API int lgbcu_set_label_gain(LgbCuContext* ctx, const double* label_gain, int32_t n);
@@ -322,6 +331,8 @@ LGBCU_API int lgbcu_valid_copy_score(LgbCuContext* ctx, int32_t set, double* out
 #define LGBCU_METRIC_NDCG 4
 #define LGBCU_METRIC_MULTI_LOGLOSS 5   /* `sigmoid` > 0: softmax the K raw scores first (the objective's ConvertOutput) */
 #define LGBCU_METRIC_MULTI_ERROR 6     /* `sigmoid` = +top_k (softmax first) or -top_k (scores as they are) */
+#define LGBCU_METRIC_L1 7
+#define LGBCU_METRIC_QUANTILE 8        /* `sigmoid` = alpha */
 LGBCU_API int lgbcu_eval_set_ndcg(LgbCuContext* ctx, int32_t set, const int32_t* eval_at, int32_t num_eval,
                                   const double* inv_max_dcg, const float* query_weight, const double* label_gain,
                                   int32_t num_label_gain, const double* discount, int32_t num_discount);

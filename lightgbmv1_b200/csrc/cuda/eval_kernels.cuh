@@ -43,6 +43,11 @@ __global__ void __launch_bounds__(EVAL_THREADS) k_eval_pointwise(int n, int kind
     double loss;
     if (kind == 0) {
       loss = (s - y) * (s - y);
+    } else if (kind == 2) {          // L1Metric::LossOnPoint (regression_metric.hpp:177)
+      loss = fabs(s - y);
+    } else if (kind == 3) {          // QuantileMetric::LossOnPoint (:157-164); `sigmoid` carries config.alpha
+      const double delta = y - s;
+      loss = delta < 0 ? (sigmoid - 1.0f) * delta : sigmoid * delta;
     } else {
       // BinaryLogloss::ConvertOutput; sigmoid <= 0 = no objective (custom): the score is taken as the probability
       const double prob = sigmoid > 0.0 ? 1.0f / (1.0f + exp(-sigmoid * s)) : s;

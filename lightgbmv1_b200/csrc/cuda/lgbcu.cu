@@ -221,6 +221,10 @@ struct LgbCuContext {
   // per-row state
   float2* d_gh = nullptr;  // interleaved (g, h) of the current iteration
   float *d_grad = nullptr, *d_hess = nullptr, *d_label = nullptr, *d_weight = nullptr;
+  // RenewTreeOutput scratch (renew_kernels.cuh)
+  double* d_renew_key[2] = {nullptr, nullptr}; float* d_renew_w[2] = {nullptr, nullptr}; double* d_renew_cdf = nullptr;
+  double* d_renew_wd = nullptr; int* d_renew_seg = nullptr; int renew_cap = 0;
+  int* d_renew_begin = nullptr; int* d_renew_end = nullptr; double* d_renew_out = nullptr; int* d_renew_nonempty = nullptr; int renew_leaf_cap = 0;
   // multiclass: K score / gradient / hessian planes ([class][row], as the reference's ScoreUpdater and gradients_ lay
   // them out); d_score / d_grad / d_hess always point at the CURRENT class's plane (lgbcu_set_class), so that every
   // kernel below trains and scores "a" class without knowing there are several
@@ -700,7 +704,8 @@ int lgbcu_destroy(LgbCuContext* c) {
                   c->d_feat_best, c->d_ctl, c->d_records, c->d_leaf_value, c->d_export, c->d_tree_i32, c->d_tree_i8,
                   c->d_tree_f64, c->d_rows, c->d_scratch, c->d_parent_split, c->d_mfb_fix, c->d_feat_key, c->d_leaf_key, c->d_spec, c->d_expanded,
                   c->d_bag_state, c->d_bag_bits, c->d_bag_tile, c->d_bag_ctl, c->d_bag, c->d_goss, c->d_goss_amp, c->d_goss_mult,
-                  c->d_cand_send, c->d_cand_all};
+                  c->d_cand_send, c->d_cand_all, c->d_renew_key[0], c->d_renew_key[1], c->d_renew_w[0], c->d_renew_w[1], c->d_renew_cdf,
+                  c->d_renew_wd, c->d_renew_seg, c->d_renew_begin, c->d_renew_end, c->d_renew_out, c->d_renew_nonempty};
   for (void* p : ptrs) if (p) lgb_dev_free(p);
   if (c->h_records) lgb_host_free(c->h_records);
   if (c->h_ctl) lgb_host_free(c->h_ctl);
@@ -886,7 +891,7 @@ int lgbcu_set_query(LgbCuContext* c, const int32_t* boundaries, int32_t num_quer
 
 int lgbcu_set_objective(LgbCuContext* c, int kind, double p0, double p1, double p2) {
   NEED(c, "lgbcu: NULL context");
-  NEED(kind >= LGBCU_OBJ_NONE && kind <= LGBCU_OBJ_MULTICLASS, "lgbcu_set_objective: unknown kind %d", kind);
+  NEED(kind >= LGBCU_OBJ_NONE && kind <= LGBCU_OBJ_QUANTILE, "lgbcu_set_objective: unknown kind %d", kind);
   if (kind == LGBCU_OBJ_BINARY || kind == LGBCU_OBJ_LAMBDARANK) NEED(p0 > 0, "Sigmoid parameter %f should be greater than zero", p0);
   c->objective = kind; c->obj_p[0] = p0; c->obj_p[1] = p1; c->obj_p[2] = p2;
   c->rank_ready = false;
@@ -945,6 +950,10 @@ int lgbcu_get_gradients(LgbCuContext* c) {
   } else if (c->objective == LGBCU_OBJ_LAMBDARANK) {
     if (rank_prepare(c)) return -1;
     if (rank_launch(c)) return -1;
+  } else if (c->objective == LGBCU_OBJ_L1) {
+    LAUNCH(k_grad_l1, g, 256, 0, c->stream, c->N, c->d_score, c->d_label, w, c->d_grad, c->d_hess);
+  } else if (c->objective == LGBCU_OBJ_QUANTILE) {
+    LAUNCH(k_grad_quantile, g, 256, 0, c->stream, c->N, c->d_score, c->d_label, w, (float)c->obj_p[0], c->d_grad, c->d_hess);
   } else if (c->objective == LGBCU_OBJ_MULTICLASS) {
     NEED((int)c->obj_p[0] == c->num_class, "lgbcu_get_gradients: the objective has %d classes, the learner %d (lgbcu_set_num_class)", (int)c->obj_p[0], c->num_class);
     LAUNCH(k_grad_multiclass, g, 256, 0, c->stream, c->N, c->num_class, c->d_score_base, c->d_label, w, c->obj_p[1], c->d_grad_base, c->d_hess_base);
@@ -1552,3 +1561,6 @@ int lgbcu_comm_destroy(LgbCuContext* c) {  // detach: the communicator itself st
 #include "bagging_kernels.cuh"
 
 #include "binning_kernels.cuh"
+
+#include <cub/device/device_segmented_sort.cuh>
+#include "renew_kernels.cuh"

@@ -37,6 +37,32 @@ __global__ void k_grad_l2(int n, const double* __restrict__ score, const float* 
   }
 }
 
+// RegressionL1loss::GetGradients (src/objective/regression_objective.hpp:214-231): sign(score - label) [* w], hessian 1 [w]
+__global__ void k_grad_l1(int n, const double* __restrict__ score, const float* __restrict__ label,
+                          const float* __restrict__ weight, float* __restrict__ grad, float* __restrict__ hess) {
+  for (int i = blockIdx.x * blockDim.x + threadIdx.x; i < n; i += gridDim.x * blockDim.x) {
+    const double diff = score[i] - label[i];
+    const int sg = (diff > 0.0) - (diff < 0.0);   // Common::Sign
+    if (weight == nullptr) { grad[i] = (float)sg; hess[i] = 1.0f; }
+    else { grad[i] = (float)(sg * weight[i]); hess[i] = weight[i]; }
+  }
+}
+
+// RegressionQuantileloss::GetGradients (:491-516): alpha is held as a float; delta is the float of (score - label)
+__global__ void k_grad_quantile(int n, const double* __restrict__ score, const float* __restrict__ label,
+                                const float* __restrict__ weight, float alpha, float* __restrict__ grad, float* __restrict__ hess) {
+  for (int i = blockIdx.x * blockDim.x + threadIdx.x; i < n; i += gridDim.x * blockDim.x) {
+    const float delta = (float)(score[i] - label[i]);
+    if (weight == nullptr) {
+      grad[i] = delta >= 0 ? (1.0f - alpha) : -alpha;
+      hess[i] = 1.0f;
+    } else {
+      grad[i] = delta >= 0 ? (float)((1.0f - alpha) * weight[i]) : (float)(-alpha * weight[i]);
+      hess[i] = (float)(weight[i]);
+    }
+  }
+}
+
 // MulticlassSoftmax::GetGradients (src/objective/multiclass_objective.hpp:86-130): one thread per row over the K score
 // planes (class-major, [k][n]); Common::Softmax's order of operations (max, exp(x - max) summed in class order, divide)
 __global__ void k_grad_multiclass(int n, int K, const double* __restrict__ score, const float* __restrict__ label,

@@ -238,18 +238,18 @@ int eval_auc(LgbCuContext* c, int n, const double* score, const float* label, co
 
 int lgbcu_eval(LgbCuContext* c, int32_t set, int32_t kind, double sigmoid, double* out, int32_t out_len) {
   NEED(c && out && out_len >= 1, "lgbcu_eval: bad argument");
-  NEED(kind >= LGBCU_METRIC_L2 && kind <= LGBCU_METRIC_MULTI_ERROR, "lgbcu_eval: unknown metric kind %d", kind);
+  NEED(kind >= LGBCU_METRIC_L2 && kind <= LGBCU_METRIC_QUANTILE, "lgbcu_eval: unknown metric kind %d", kind);
   USE_DEVICE(c->device);
   int n; const double* score; const float* label; const float* weight; const int* query; int nq; NdcgTables* nd;
   if (set < 0) {
     NEED(c->N > 0, "lgbcu_eval: no training data");
     n = c->N; score = c->d_score; label = c->has_label ? c->d_label : nullptr; weight = c->has_weight ? c->d_weight : nullptr;
-    if (kind >= LGBCU_METRIC_MULTI_LOGLOSS) score = c->d_score_base;
+    if (kind == LGBCU_METRIC_MULTI_LOGLOSS || kind == LGBCU_METRIC_MULTI_ERROR) score = c->d_score_base;
     query = c->d_query; nq = c->num_queries; nd = &c->train_ndcg;
   } else {
     ValidSet* v; if (valid_get(c, set, &v)) return -1;
     n = v->n; score = v->d_score; label = v->d_label; weight = v->d_weight; query = v->d_query; nq = v->num_queries; nd = &v->ndcg;
-    if (kind >= LGBCU_METRIC_MULTI_LOGLOSS) score = v->d_score_base;
+    if (kind == LGBCU_METRIC_MULTI_LOGLOSS || kind == LGBCU_METRIC_MULTI_ERROR) score = v->d_score_base;
   }
   NEED(label, "lgbcu_eval: the data set has no label");
   if (eval_scratch(c)) return -1;
@@ -271,7 +271,7 @@ int lgbcu_eval(LgbCuContext* c, int32_t set, int32_t kind, double sigmoid, doubl
   if (eval_sum_weights(c, n, weight, &sum_w)) return -1;
   if (kind == LGBCU_METRIC_AUC) return eval_auc(c, n, score, label, weight, sum_w, out);
   const int grid = std::min(EVAL_MAX_BLOCKS, (n + EVAL_THREADS - 1) / EVAL_THREADS);
-  if (kind >= LGBCU_METRIC_MULTI_LOGLOSS) {
+  if (kind == LGBCU_METRIC_MULTI_LOGLOSS || kind == LGBCU_METRIC_MULTI_ERROR) {
     // `sigmoid` carries the parameter: multi_logloss > 0 = apply the objective's softmax; multi_error: top_k, negative
     // when the scores are to be taken as they are (no objective)
     const int softmax = kind == LGBCU_METRIC_MULTI_LOGLOSS ? (sigmoid > 0.0 ? 1 : 0) : (sigmoid > 0.0 ? 1 : 0);
@@ -285,7 +285,8 @@ int lgbcu_eval(LgbCuContext* c, int32_t set, int32_t kind, double sigmoid, doubl
     out[0] = c->h_eval_out[0] / sum_w;
     return 0;
   }
-  LAUNCH(k_eval_pointwise, grid, EVAL_THREADS, 0, c->stream, n, kind == LGBCU_METRIC_BINARY_LOGLOSS ? 1 : 0, sigmoid, score,
+  const int pk = kind == LGBCU_METRIC_BINARY_LOGLOSS ? 1 : kind == LGBCU_METRIC_L1 ? 2 : kind == LGBCU_METRIC_QUANTILE ? 3 : 0;
+  LAUNCH(k_eval_pointwise, grid, EVAL_THREADS, 0, c->stream, n, pk, sigmoid, score,
          label, weight, c->d_eval_partial);
   LAUNCH(k_eval_final, 1, EVAL_THREADS, 0, c->stream, grid, 1, c->d_eval_partial, c->d_eval_out);
   CU(cudaGetLastError());

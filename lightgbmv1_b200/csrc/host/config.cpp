@@ -110,6 +110,7 @@ std::string ObjectiveAlias(std::string t) {
       t == "l2_root" || t == "root_mean_squared_error" || t == "rmse") return "regression";
   if (t == "none" || t == "null" || t == "custom" || t == "na") return "custom";
   if (t == "multiclass" || t == "softmax") return "multiclass";
+  if (t == "regression_l1" || t == "mean_absolute_error" || t == "l1" || t == "mae") return "regression_l1";
   return t;
 }
 
@@ -241,6 +242,8 @@ void Config::Set(const std::unordered_map<std::string, std::string>& p) {
   GetBool(p, "feature_pre_filter", &feature_pre_filter);
   GetBool(p, "enable_bundle", &enable_bundle);
   GetDouble(p, "sigmoid", &sigmoid);
+  GetDouble(p, "alpha", &alpha);
+  if (alpha <= 0.0) Log::Fatal("alpha should be > 0");
   GetBool(p, "is_unbalance", &is_unbalance);
   GetDouble(p, "scale_pos_weight", &scale_pos_weight);
   GetBool(p, "boost_from_average", &boost_from_average);

@@ -55,6 +55,7 @@ struct Config {
   bool enable_bundle = true;
   // objective
   double sigmoid = 1.0;
+  double alpha = 0.9;   // quantile objective / metric (config.h:815)
   bool is_unbalance = false;
   double scale_pos_weight = 1.0;
   bool boost_from_average = true;

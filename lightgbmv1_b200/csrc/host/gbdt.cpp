@@ -118,13 +118,15 @@ GBDT::GBDT(const Dataset* train, const Config& config)
       spec.kind = LGBCU_METRIC_NDCG;
       for (int k : eval_at_) spec.names.push_back("ndcg@" + std::to_string(k));
     }
+    else if (m == "l1") { spec.kind = LGBCU_METRIC_L1; spec.names = {"l1"}; }
+    else if (m == "quantile") { spec.kind = LGBCU_METRIC_QUANTILE; spec.names = {"quantile"}; }
     else if (m == "multi_logloss") { spec.kind = LGBCU_METRIC_MULTI_LOGLOSS; spec.names = {"multi_logloss"}; }
     else if (m == "multi_error") {
       spec.kind = LGBCU_METRIC_MULTI_ERROR;
       spec.names = {config_.multi_error_top_k == 1 ? std::string("multi_error") : "multi_error@" + std::to_string(config_.multi_error_top_k)};
     }
     else if (m == "custom") continue;
-    else Log::Fatal("metric=%s is outside this library's path (l2, rmse, binary_logloss, auc, ndcg, multi_logloss, multi_error)", m.c_str());
+    else Log::Fatal("metric=%s is outside this library's path (l2, rmse, l1, quantile, binary_logloss, auc, ndcg, multi_logloss, multi_error)", m.c_str());
     if ((spec.kind == LGBCU_METRIC_MULTI_LOGLOSS || spec.kind == LGBCU_METRIC_MULTI_ERROR) != (num_tree_per_iteration_ > 1))
       Log::Fatal("Multiclass objective and metrics don't match");
     metrics_.push_back(spec);
@@ -324,6 +326,21 @@ bool GBDT::TrainOneIter(const float* grad, const float* hess) {
     }
     if (tree->num_leaves() > 1) {
       should_continue = true;
+      // RenewTreeOutput (serial_tree_learner.cpp:661-699): percentile objectives replace every leaf's Newton step by
+      // the (weighted) percentile of label - score over the rows the tree grew on, before shrinkage
+      if (objective_ && objective_->IsRenewTreeOutput()) {
+        const int nl = tree->num_leaves();
+        std::vector<double> out(nl); std::vector<int32_t> has(nl);
+        Check(lgbcu_renew_leaf_outputs(ctx_, nl, objective_->RenewAlpha(), objective_->RenewAlphaIsFloat() ? 1 : 0, out.data(), has.data()));
+        if (data_parallel_) {   // Network::GlobalSum of the outputs and of "this machine holds rows of the leaf"
+          std::vector<double> v(2 * static_cast<size_t>(nl));
+          for (int i = 0; i < nl; ++i) { v[i] = has[i] ? out[i] : 0.0; v[nl + i] = has[i] ? 1.0 : 0.0; }
+          for (size_t o = 0; o < v.size(); o += 64) Check(lgbcu_comm_allreduce_sum_f64(ctx_, v.data() + o, static_cast<int>(std::min<size_t>(64, v.size() - o))));
+          for (int i = 0; i < nl; ++i) tree->SetLeafOutput(i, v[i] / v[nl + i]);
+        } else {
+          for (int i = 0; i < nl; ++i) tree->SetLeafOutput(i, out[i]);
+        }
+      }
       tree->Shrinkage(shrinkage_rate_);
       // UpdateScore (gbdt.cpp:458-478): in-bag rows through the partition, out-of-bag rows by walking the tree
       Check(lgbcu_add_score_by_partition(ctx_, tree->leaf_values().data(), tree->num_leaves()));
@@ -502,6 +519,7 @@ std::vector<double> GBDT::GetEvalAt(int data_idx) {
     double buf[64];
     // metrics convert the raw score through the objective (ObjectiveFunction::ConvertOutput): a sigmoid for binary
     double sig = (objective_ && std::string(objective_->Name()) == "binary") ? config_.sigmoid : 0.0;
+    if (m.kind == LGBCU_METRIC_QUANTILE) sig = config_.alpha;
     if (m.kind == LGBCU_METRIC_MULTI_LOGLOSS) sig = objective_ ? 1.0 : 0.0;                                       // softmax first
     if (m.kind == LGBCU_METRIC_MULTI_ERROR) sig = (objective_ ? 1.0 : -1.0) * config_.multi_error_top_k;
     Check(lgbcu_eval(ctx_, set, m.kind, sig, buf, 64));

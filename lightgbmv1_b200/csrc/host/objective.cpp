@@ -1,6 +1,10 @@
 #include "objective.h"
 
+#include <algorithm>
 #include <cmath>
+#include <functional>
+#include <sstream>
+#include <vector>
 
 namespace lgb {
 namespace {
@@ -124,6 +128,69 @@ class Lambdarank : public Objective {
 
 }  // namespace
 
+// PercentileFun / WeightedPercentileFun (src/objective/regression_objective.hpp:18-88) over the labels, for the
+// BoostFromScore of the percentile objectives; T = label_t as there.  `one_minus_alpha_times_cnt` is formed by the
+// caller in the arithmetic its objective uses (double for L1's 0.5, float for the quantile objective's float alpha).
+static double LabelPercentile(const label_t* label, data_size_t n, double float_pos) {
+  if (n <= 1) return label[0];
+  std::vector<label_t> v(label, label + n);
+  const data_size_t pos = static_cast<data_size_t>(float_pos);
+  if (pos < 1) return *std::max_element(v.begin(), v.end());
+  if (pos >= n) return *std::min_element(v.begin(), v.end());
+  const double bias = float_pos - pos;
+  // the pos-th and (pos+1)-th largest values, whichever selection the reference's two branches run
+  std::nth_element(v.begin(), v.begin() + (pos - 1), v.end(), std::greater<label_t>());
+  const label_t v1 = v[pos - 1];
+  const label_t v2 = *std::max_element(v.begin() + pos, v.end());
+  return static_cast<label_t>(v1 - (v1 - v2) * bias);
+}
+static double LabelWeightedPercentile(const label_t* label, const label_t* weight, data_size_t n, double alpha) {
+  if (n <= 1) return label[0];
+  std::vector<data_size_t> idx(n);
+  for (data_size_t i = 0; i < n; ++i) idx[i] = i;
+  std::stable_sort(idx.begin(), idx.end(), [&](data_size_t a, data_size_t b) { return label[a] < label[b]; });
+  std::vector<double> cdf(n);
+  cdf[0] = weight[idx[0]];
+  for (data_size_t i = 1; i < n; ++i) cdf[i] = cdf[i - 1] + weight[idx[i]];
+  const double threshold = cdf[n - 1] * alpha;
+  size_t pos = std::upper_bound(cdf.begin(), cdf.end(), threshold) - cdf.begin();
+  pos = std::min(pos, static_cast<size_t>(n - 1));
+  if (pos == 0 || pos == static_cast<size_t>(n - 1)) return label[idx[pos]];
+  const label_t v1 = label[idx[pos - 1]], v2 = label[idx[pos]];
+  if (cdf[pos + 1] - cdf[pos] >= 1.0f) return static_cast<label_t>((threshold - cdf[pos]) / (cdf[pos + 1] - cdf[pos]) * (v2 - v1) + v1);
+  return static_cast<label_t>(v2);
+}
+
+// src/objective/regression_objective.hpp (RegressionL1loss :204-283, RegressionQuantileloss :479-571)
+class RegressionPercentile : public Objective {
+ public:
+  RegressionPercentile(const Config& c, bool quantile) : quantile_(quantile), alpha_f_(static_cast<float>(c.alpha)) {
+    if (c.reg_sqrt) Log::Fatal("reg_sqrt is outside this library's path");
+    if (quantile_ && !(alpha_f_ > 0 && alpha_f_ < 1)) Log::Fatal("Check failed: alpha_ > 0 && alpha_ < 1");
+  }
+  void Init(const Metadata& meta, data_size_t n, const SumSync&) override {
+    num_data_ = n; label_ = meta.label.data(); weights_ = meta.weights.empty() ? nullptr : meta.weights.data();
+    if (meta.label.empty()) Log::Fatal("Label should not be NULL");
+  }
+  void Configure(LgbCuContext* ctx) const override {
+    Check(lgbcu_set_objective(ctx, quantile_ ? LGBCU_OBJ_QUANTILE : LGBCU_OBJ_L1, quantile_ ? alpha_f_ : 0.5, 0, 0));
+  }
+  double BoostFromScore(int) const override {
+    if (weights_) return LabelWeightedPercentile(label_, weights_, num_data_, quantile_ ? static_cast<double>(alpha_f_) : 0.5);
+    const double float_pos = quantile_ ? static_cast<double>((1.0f - alpha_f_) * num_data_) : (1.0f - 0.5) * num_data_;
+    return LabelPercentile(label_, num_data_, float_pos);
+  }
+  bool IsRenewTreeOutput() const override { return true; }
+  double RenewAlpha() const override { return quantile_ ? static_cast<double>(alpha_f_) : 0.5; }
+  bool RenewAlphaIsFloat() const override { return quantile_; }
+  std::string ToString() const override { return quantile_ ? "quantile" : "regression_l1"; }
+  const char* Name() const override { return quantile_ ? "quantile" : "regression_l1"; }
+
+ private:
+  bool quantile_; float alpha_f_;
+  data_size_t num_data_ = 0; const label_t* label_ = nullptr; const label_t* weights_ = nullptr;
+};
+
 // src/objective/multiclass_objective.hpp (MulticlassSoftmax)
 class MulticlassSoftmax : public Objective {
  public:
@@ -181,11 +248,13 @@ class MulticlassSoftmax : public Objective {
 
 Objective* Objective::Create(const Config& c) {
   if (c.objective == "multiclass") return new MulticlassSoftmax(c);
+  if (c.objective == "regression_l1") return new RegressionPercentile(c, false);
+  if (c.objective == "quantile") return new RegressionPercentile(c, true);
   if (c.objective == "binary") return new BinaryLogloss(c);
   if (c.objective == "regression") return new RegressionL2(c);
   if (c.objective == "lambdarank") return new Lambdarank(c);
   if (c.objective == "custom") return nullptr;
-  Log::Fatal("objective=%s is outside this library's path (binary, regression/l2, lambdarank, multiclass, custom)", c.objective.c_str());
+  Log::Fatal("objective=%s is outside this library's path (binary, regression/l2, regression_l1, quantile, lambdarank, multiclass, custom)", c.objective.c_str());
 }
 
 }  // namespace lgb

@@ -24,6 +24,11 @@ class Objective {
   virtual void Configure(LgbCuContext* ctx) const = 0;  // push kind + parameters to the device learner
   virtual double BoostFromScore(int class_id = 0) const = 0;
   virtual bool NeedTrain(int class_id = 0) const { return true; }   // ObjectiveFunction::ClassNeedTrain
+  // ObjectiveFunction::IsRenewTreeOutput: leaf values are recomputed as a percentile of the residuals after a tree is
+  // grown (lgbcu_renew_leaf_outputs); RenewAlpha / RenewAlphaIsFloat say which one and in which arithmetic
+  virtual bool IsRenewTreeOutput() const { return false; }
+  virtual double RenewAlpha() const { return 0.5; }
+  virtual bool RenewAlphaIsFloat() const { return false; }
   virtual int NumModelPerIteration() const { return 1; }           // trees (= score planes) per boosting iteration
   // ConvertOutput works on one row's NumModelPerIteration() raw scores
   virtual data_size_t NumPositiveData() const { return 0; }  // rows of this machine with label > 0 (balanced bagging)

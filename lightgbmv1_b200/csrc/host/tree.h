@@ -27,6 +27,8 @@ class Tree {
 
   int num_leaves() const { return num_leaves_; }
   double leaf_value(int i) const { return leaf_value_[i]; }
+  // Tree::SetLeafOutput (tree.h:92-94): MaybeRoundToZero(output)
+  void SetLeafOutput(int leaf, double v) { leaf_value_[leaf] = (v >= -kZeroThreshold && v <= kZeroThreshold) ? 0 : v; }
   const std::vector<double>& leaf_values() const { return leaf_value_; }
   const std::vector<int>& split_feature_inner() const { return split_feature_inner_; }
   const std::vector<int>& split_feature() const { return split_feature_; }
