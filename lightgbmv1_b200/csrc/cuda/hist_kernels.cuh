@@ -27,7 +27,9 @@
 //                    every lane then reads one 16-byte broadcast per row (row offset, g low, h low, packed high
 //                    words) and fetches ITS OWN bin of that row straight from the row-major matrix (32 lanes x 1 byte =
 //                    the row's 32-byte sector, one L1 wavefront, 16 loads in flight per warp): no transposition
-//                    through shared memory.  Shared-memory pipe per row: 1 LDS + 1 LDG + 4 ATOMS wavefronts.
+//                    through shared memory.  L1 / shared-memory data pipe per row (ncu): 4.04 ATOMS + 2.02 LDS (a
+//                    16-byte broadcast is two wavefronts) + ~1.3 for the bin bytes and the staging stores = ~7.7
+//                    wavefronts at ~1 per clock and SM: this pipe, not HBM, bounds the kernel.
 //                    The blocks of a cluster (2) work on row slices of the same feature group, sum their
 //                    sub-histograms through distributed shared memory and flush once with REDG.ADD.64 (zero entries
 //                    skipped).

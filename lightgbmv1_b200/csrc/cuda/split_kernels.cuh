@@ -120,32 +120,11 @@ __device__ __forceinline__ i64 warp_sum(i64 v) {
   return v;
 }
 
-// One thread walks a shared-memory array in index order accumulating two independent fp64 chains (gradient,
-// hessian) exactly as a sequential CPU loop would; operands are fetched 8 at a time so that only the DADD latency
-// is on the critical path.  `sign` = +1 adds, -1 subtracts (x - v is computed as x + (-v): identical in IEEE).
-// Entries equal to `skip_t` contribute +0.0, which leaves a running sum bit-unchanged.
-template <int DIR>
-__device__ __forceinline__ void chain2(const double* __restrict__ g, const double* __restrict__ h, double* og, double* oh,
-                                       int t_first, int t_last, int skip_t, double sign, double* ag_io, double* ah_io) {
-  double ag = *ag_io, ah = *ah_io;
-  const int count = DIR > 0 ? t_last - t_first + 1 : t_first - t_last + 1;
-  for (int base = 0; base < count; base += 8) {
-    double vg[8], vh[8];
-#pragma unroll
-    for (int k = 0; k < 8; ++k) {
-      const int t = t_first + DIR * (base + k);
-      const bool ok = (base + k) < count && t != skip_t;
-      vg[k] = ok ? sign * g[t] : 0.0;
-      vh[k] = ok ? sign * h[t] : 0.0;
-    }
-#pragma unroll
-    for (int k = 0; k < 8; ++k) {
-      ag += vg[k]; ah += vh[k];
-      if (og && (base + k) < count) { const int t = t_first + DIR * (base + k); og[t] = ag; oh[t] = ah; }
-    }
-  }
-  *ag_io = ag; *ah_io = ah;
-}
+// One thread walks a shared-memory array in index order accumulating an fp64 chain exactly as a sequential CPU loop
+// would; operands are fetched 8 at a time so that only the DADD latency is on the critical path.  `sign` = +1 adds,
+// -1 subtracts (x - v is computed as x + (-v): identical in IEEE).  Entries equal to `skip_t` contribute +0.0, which
+// leaves a running sum bit-unchanged.  (Used for the implicit-first-bin pre-pass; the two main chains walk a
+// pre-laid-out input, chain_lin below.)
 template <int DIR>
 __device__ __forceinline__ void chain1(const double* __restrict__ h, double* oh, int t_first, int t_last, int skip_t,
                                        double sign, double* ah_io) {
@@ -193,27 +172,6 @@ __device__ __forceinline__ void chain_lin(const double* __restrict__ in, double*
     if (i + k < count) { ah += v[k]; out0[DIR * (i + k)] = ah; }
   *ah_io = ah;
 }
-template <int DIR>
-__device__ __forceinline__ void chain_cnt(const int* __restrict__ c, int* out, int t_first, int t_last, int skip_t,
-                                          int sign, int* acc_io) {
-  int acc = *acc_io;
-  const int count = DIR > 0 ? t_last - t_first + 1 : t_first - t_last + 1;
-  for (int base = 0; base < count; base += 8) {
-    int v[8];
-#pragma unroll
-    for (int k = 0; k < 8; ++k) {
-      const int t = t_first + DIR * (base + k);
-      v[k] = ((base + k) < count && t != skip_t) ? sign * c[t] : 0;
-    }
-#pragma unroll
-    for (int k = 0; k < 8; ++k) {
-      acc += v[k];
-      if (out && (base + k) < count) out[t_first + DIR * (base + k)] = acc;
-    }
-  }
-  *acc_io = acc;
-}
-
 // SplitKey::pad = inner feature | threshold << 20 | default_left << 29 (bins are 8-bit, so a threshold fits 9 bits)
 #define KEY_FEAT_BITS 20
 __device__ __forceinline__ int key_pack(int feature, int threshold, int default_left) {
