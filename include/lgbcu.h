@@ -44,7 +44,7 @@ typedef struct LgbCuContext LgbCuContext;
 enum { LGBCU_MISSING_NONE = 0, LGBCU_MISSING_ZERO = 1, LGBCU_MISSING_NAN = 2 };
 /* objective kinds implemented on device (src/objective/) */
 enum { LGBCU_OBJ_NONE = 0, LGBCU_OBJ_BINARY = 1, LGBCU_OBJ_L2 = 2, LGBCU_OBJ_LAMBDARANK = 3, LGBCU_OBJ_MULTICLASS = 4,
-       LGBCU_OBJ_L1 = 5, LGBCU_OBJ_QUANTILE = 6 };
+       LGBCU_OBJ_L1 = 5, LGBCU_OBJ_QUANTILE = 6, LGBCU_OBJ_MULTICLASSOVA = 7 };
 /* histogram kernel selection (LGBCU_HIST_AUTO picks by leaf size) */
 enum { LGBCU_HIST_AUTO = 0, LGBCU_HIST_GLOBAL_ATOMIC = 1, LGBCU_HIST_WARP_PRIVATE = 2 };
 
@@ -188,6 +188,10 @@ LGBCU_API int lgbcu_renew_leaf_outputs(LgbCuContext* ctx, int32_t num_leaves, do
                                        double* leaf_values, int32_t* leaf_nonempty);
 LGBCU_API int lgbcu_set_num_class(LgbCuContext* ctx, int32_t num_class);
 LGBCU_API int lgbcu_set_class(LgbCuContext* ctx, int32_t class_id);
+/* multiclassova (multiclass_objective.hpp:186-276; lgbcu_set_objective p0 = num_class, p1 = sigmoid): one binary logloss
+ * per class whose positive rows are (int)label == class; neg_pos = that class's (label weight of the negatives, of the
+ * positives) pairs, [num_class][2] (is_unbalance / scale_pos_weight, binary_objective.hpp:76-96) */
+LGBCU_API int lgbcu_set_ova_label_weights(LgbCuContext* ctx, const double* neg_pos, int32_t num_class);
 LGBCU_API int lgbcu_set_label_gain(LgbCuContext* ctx, const double* label_gain, int32_t n);
 LGBCU_API int lgbcu_get_gradients(LgbCuContext* ctx);                      /* score -> grad,hess (device) */
 LGBCU_API int lgbcu_set_gradients(LgbCuContext* ctx, const float* grad, const float* hess, int32_t n);

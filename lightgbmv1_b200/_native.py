@@ -72,7 +72,7 @@ LGBCU_SYMBOLS = [
     "lgbcu_set_score", "lgbcu_add_score_const", "lgbcu_copy_score", "lgbcu_add_score_by_partition", "lgbcu_add_score_by_tree",
     "lgbcu_begin_tree", "lgbcu_hist_build", "lgbcu_hist_read", "lgbcu_num_total_bin", "lgbcu_hist_subtract",
     "lgbcu_find_best_split", "lgbcu_partition", "lgbcu_leaf_indices", "lgbcu_set_leaf_sums",
-    "lgbcu_get_leaf_sums", "lgbcu_train_tree", "lgbcu_comm_unique_id", "lgbcu_comm_init", "lgbcu_comm_destroy", "lgbcu_comm_release_all", "lgbcu_bagging_reset", "lgbcu_bagging", "lgbcu_bagging_balanced", "lgbcu_copy_bag", "lgbcu_goss_scores", "lgbcu_goss_apply", "lgbcu_set_num_class", "lgbcu_set_class", "lgbcu_renew_leaf_outputs", "lgbcu_bin_matrix", "lgbcu_binned_copy_to_host", "lgbcu_binned_device", "lgbcu_binned_free", "lgbcu_set_dataset_binned", "lgbcu_comm_allreduce_sum_f64",
+    "lgbcu_get_leaf_sums", "lgbcu_train_tree", "lgbcu_comm_unique_id", "lgbcu_comm_init", "lgbcu_comm_destroy", "lgbcu_comm_release_all", "lgbcu_bagging_reset", "lgbcu_bagging", "lgbcu_bagging_balanced", "lgbcu_copy_bag", "lgbcu_goss_scores", "lgbcu_goss_apply", "lgbcu_set_num_class", "lgbcu_set_class", "lgbcu_set_ova_label_weights", "lgbcu_renew_leaf_outputs", "lgbcu_bin_matrix", "lgbcu_binned_copy_to_host", "lgbcu_binned_device", "lgbcu_binned_free", "lgbcu_set_dataset_binned", "lgbcu_comm_allreduce_sum_f64",
     "lgbcu_profile_enable", "lgbcu_profile_read", "lgbcu_partition_rows_noalloc", "lgbcu_profile_phases", "lgbcu_pin_host_buffer", "lgbcu_unpin_host_buffer", "lgbcu_valid_create", "lgbcu_valid_set_label",
     "lgbcu_valid_set_weight", "lgbcu_valid_set_query", "lgbcu_valid_set_score", "lgbcu_valid_add_const", "lgbcu_valid_add_tree",
     "lgbcu_valid_copy_score", "lgbcu_eval_set_ndcg", "lgbcu_eval",

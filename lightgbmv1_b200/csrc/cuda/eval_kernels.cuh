@@ -64,7 +64,7 @@ __global__ void __launch_bounds__(EVAL_THREADS) k_eval_pointwise(int n, int kind
 // converted by the objective's softmax (softmax = 0: no objective, the scores are taken as they are), then
 // kind 0: multi_logloss  -log(max(p[label], kEpsilon))          (MultiSoftmaxLoglossMetric::LossOnPoint, :167-175)
 // kind 1: multi_error@top_k: 1 if more than top_k classes score >= the label's class   (MultiErrorMetric, :142-151)
-__global__ void __launch_bounds__(EVAL_THREADS) k_eval_multiclass(int n, int K, int kind, int top_k, int softmax,
+__global__ void __launch_bounds__(EVAL_THREADS) k_eval_multiclass(int n, int K, int kind, int top_k, int softmax, double ova_sigmoid,
                                                                   const double* __restrict__ score, const float* __restrict__ label,
                                                                   const float* __restrict__ weight, double* __restrict__ partial) {
   __shared__ double s_warp[EVAL_THREADS / 32];
@@ -75,8 +75,9 @@ __global__ void __launch_bounds__(EVAL_THREADS) k_eval_multiclass(int n, int K, 
     for (int k = 1; k < K; ++k) wmax = fmax(score[(size_t)n * k + i], wmax);
     double wsum = 0.0;
     if (softmax) for (int k = 0; k < K; ++k) wsum += exp(score[(size_t)n * k + i] - wmax);
+    // ova_sigmoid > 0: MulticlassOVA::ConvertOutput, a sigmoid per class (multiclass_objective.hpp:239-243)
     const double raw_l = score[(size_t)n * lab + i];
-    const double pl = softmax ? exp(raw_l - wmax) / wsum : raw_l;
+    const double pl = softmax ? exp(raw_l - wmax) / wsum : ova_sigmoid > 0.0 ? 1.0f / (1.0f + exp(-ova_sigmoid * raw_l)) : raw_l;
     double loss;
     if (kind == 0) {
       loss = pl > LGB_EPS ? -log(pl) : -log(LGB_EPS);
@@ -84,7 +85,7 @@ __global__ void __launch_bounds__(EVAL_THREADS) k_eval_multiclass(int n, int K, 
       int num_larger = 0;
       for (int k = 0; k < K; ++k) {
         const double raw = score[(size_t)n * k + i];
-        const double pk = softmax ? exp(raw - wmax) / wsum : raw;
+        const double pk = softmax ? exp(raw - wmax) / wsum : ova_sigmoid > 0.0 ? 1.0f / (1.0f + exp(-ova_sigmoid * raw)) : raw;
         if (pk >= pl) ++num_larger;
       }
       loss = num_larger > top_k ? 1.0 : 0.0;

@@ -229,6 +229,7 @@ struct LgbCuContext {
   // them out); d_score / d_grad / d_hess always point at the CURRENT class's plane (lgbcu_set_class), so that every
   // kernel below trains and scores "a" class without knowing there are several
   int num_class = 1, cur_class = 0;
+  std::vector<double> ova_w;   // multiclassova: (label weight of the negative, of the positive) per class
   float *d_grad_base = nullptr, *d_hess_base = nullptr; double* d_score_base = nullptr;
   bool has_weight = false, has_label = false;
   double* d_score = nullptr;
@@ -891,7 +892,7 @@ int lgbcu_set_query(LgbCuContext* c, const int32_t* boundaries, int32_t num_quer
 
 int lgbcu_set_objective(LgbCuContext* c, int kind, double p0, double p1, double p2) {
   NEED(c, "lgbcu: NULL context");
-  NEED(kind >= LGBCU_OBJ_NONE && kind <= LGBCU_OBJ_QUANTILE, "lgbcu_set_objective: unknown kind %d", kind);
+  NEED(kind >= LGBCU_OBJ_NONE && kind <= LGBCU_OBJ_MULTICLASSOVA, "lgbcu_set_objective: unknown kind %d", kind);
   if (kind == LGBCU_OBJ_BINARY || kind == LGBCU_OBJ_LAMBDARANK) NEED(p0 > 0, "Sigmoid parameter %f should be greater than zero", p0);
   c->objective = kind; c->obj_p[0] = p0; c->obj_p[1] = p1; c->obj_p[2] = p2;
   c->rank_ready = false;
@@ -926,6 +927,12 @@ int lgbcu_set_num_class(LgbCuContext* c, int32_t num_class) {
   return 0;
 }
 
+int lgbcu_set_ova_label_weights(LgbCuContext* c, const double* neg_pos, int32_t num_class) {
+  NEED(c && neg_pos && num_class >= 1, "lgbcu_set_ova_label_weights: bad argument");
+  c->ova_w.assign(neg_pos, neg_pos + 2 * (size_t)num_class);
+  return 0;
+}
+
 int lgbcu_set_class(LgbCuContext* c, int32_t k) {
   NEED(c && k >= 0 && k < c->num_class, "lgbcu_set_class: class %d out of range", (int)k);
   c->cur_class = k;
@@ -950,6 +957,13 @@ int lgbcu_get_gradients(LgbCuContext* c) {
   } else if (c->objective == LGBCU_OBJ_LAMBDARANK) {
     if (rank_prepare(c)) return -1;
     if (rank_launch(c)) return -1;
+  } else if (c->objective == LGBCU_OBJ_MULTICLASSOVA) {
+    NEED((int)c->obj_p[0] == c->num_class && (int)c->ova_w.size() == 2 * c->num_class, "lgbcu_get_gradients: multiclassova needs lgbcu_set_num_class and lgbcu_set_ova_label_weights");
+    for (int k = 0; k < c->num_class; ++k) {   // one BinaryLogloss per class on its own planes
+      const size_t off = (size_t)k * c->N;
+      LAUNCH(k_grad_binary, g, 256, 0, c->stream, c->N, c->d_score_base + off, c->d_label, w, c->obj_p[1], c->ova_w[2 * k], c->ova_w[2 * k + 1],
+             c->d_grad_base + off, c->d_hess_base + off, k);
+    }
   } else if (c->objective == LGBCU_OBJ_L1) {
     LAUNCH(k_grad_l1, g, 256, 0, c->stream, c->N, c->d_score, c->d_label, w, c->d_grad, c->d_hess);
   } else if (c->objective == LGBCU_OBJ_QUANTILE) {

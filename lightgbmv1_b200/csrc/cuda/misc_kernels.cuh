@@ -6,9 +6,11 @@
 // BinaryLogloss::GetGradients (src/objective/binary_objective.hpp:102-133)
 __global__ void k_grad_binary(int n, const double* __restrict__ score, const float* __restrict__ label,
                               const float* __restrict__ weight, double sigmoid, double w_neg, double w_pos,
-                              float* __restrict__ grad, float* __restrict__ hess) {
+                              float* __restrict__ grad, float* __restrict__ hess, int pos_class = -1) {
+  // pos_class < 0: the positive class is label > 0; otherwise it is (int)label == pos_class (MulticlassOVA's
+  // per-class BinaryLogloss, multiclass_objective.hpp:188-195)
   for (int i = blockIdx.x * blockDim.x + threadIdx.x; i < n; i += gridDim.x * blockDim.x) {
-    const int is_pos = label[i] > 0;
+    const int is_pos = pos_class < 0 ? (label[i] > 0) : ((int)label[i] == pos_class);
     const int lab = is_pos ? 1 : -1;
     const double lw = is_pos ? w_pos : w_neg;
     const double response = -lab * sigmoid / (1.0f + exp(lab * sigmoid * score[i]));

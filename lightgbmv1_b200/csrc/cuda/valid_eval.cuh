@@ -274,10 +274,12 @@ int lgbcu_eval(LgbCuContext* c, int32_t set, int32_t kind, double sigmoid, doubl
   if (kind == LGBCU_METRIC_MULTI_LOGLOSS || kind == LGBCU_METRIC_MULTI_ERROR) {
     // `sigmoid` carries the parameter: multi_logloss > 0 = apply the objective's softmax; multi_error: top_k, negative
     // when the scores are to be taken as they are (no objective)
-    const int softmax = kind == LGBCU_METRIC_MULTI_LOGLOSS ? (sigmoid > 0.0 ? 1 : 0) : (sigmoid > 0.0 ? 1 : 0);
+    const bool ova = c->objective == LGBCU_OBJ_MULTICLASSOVA;   // its ConvertOutput is a sigmoid per class, not a softmax
+    const int softmax = (sigmoid > 0.0 && !ova) ? 1 : 0;
+    const double ova_sigmoid = (sigmoid > 0.0 && ova) ? c->obj_p[1] : 0.0;
     const int top_k = kind == LGBCU_METRIC_MULTI_ERROR ? (int)std::fabs(sigmoid) : 1;
     LAUNCH(k_eval_multiclass, grid, EVAL_THREADS, 0, c->stream, n, c->num_class, kind == LGBCU_METRIC_MULTI_LOGLOSS ? 0 : 1, top_k,
-           softmax, score, label, weight, c->d_eval_partial);
+           softmax, ova_sigmoid, score, label, weight, c->d_eval_partial);
     LAUNCH(k_eval_final, 1, EVAL_THREADS, 0, c->stream, grid, 1, c->d_eval_partial, c->d_eval_out);
     CU(cudaGetLastError());
     CU(cudaMemcpyAsync(c->h_eval_out, c->d_eval_out, sizeof(double), cudaMemcpyDeviceToHost, c->stream));

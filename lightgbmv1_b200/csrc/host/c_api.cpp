@@ -35,6 +35,7 @@ struct LoadedModel {
   double sigmoid = 0.0;    // > 0: predictions are 1 / (1 + exp(-sigmoid * raw))
   int num_tree_per_iteration = 1;   // multiclass: trees (and outputs per row) per iteration
   bool softmax = false;             // "multiclass ...": predictions are the softmax of a row's raw scores
+  double ova_sigmoid = 0.0;         // "multiclassova ...": > 0, a sigmoid per class
 };
 
 struct Booster {
@@ -73,8 +74,12 @@ LoadedModel* ParseModel(const std::string& text) {
     else if (k == "feature_names") m->feature_names = SplitAny(v, " ");
     else if (k == "num_tree_per_iteration") m->num_tree_per_iteration = std::max(1, std::atoi(v.c_str()));
   }
-  if (m->objective.rfind("multiclassova", 0) == 0) Log::Fatal("multiclassova models are outside this library's path");
-  m->softmax = m->objective.rfind("multiclass", 0) == 0;
+  m->softmax = m->objective.rfind("multiclass", 0) == 0 && m->objective.rfind("multiclassova", 0) != 0;
+  if (m->objective.rfind("multiclassova", 0) == 0) {   // a sigmoid per class
+    m->ova_sigmoid = 1.0;
+    const size_t p = m->objective.find("sigmoid:");
+    if (p != std::string::npos) m->ova_sigmoid = std::strtod(m->objective.c_str() + p + 8, nullptr);
+  }
   if (m->max_feature_idx < 0) Log::Fatal("Model file doesn't specify max_feature_idx");
   if (m->objective.rfind("binary", 0) == 0) {
     m->sigmoid = 1.0;
@@ -324,6 +329,7 @@ int LGBM_BoosterPredictForMat(BoosterHandle handle, const void* data, int data_t
         for (int k = 0; k < K; ++k) sc[k] = 0.0;
         for (int t = 0; t < n_iter; ++t) for (int k = 0; k < K; ++k) sc[k] += m.trees[static_cast<size_t>(t) * K + k]->Predict(row.data());
         if (!raw && m.sigmoid > 0) sc[0] = 1.0f / (1.0f + std::exp(-m.sigmoid * sc[0]));
+        if (!raw && m.ova_sigmoid > 0) for (int k = 0; k < K; ++k) sc[k] = 1.0f / (1.0f + std::exp(-m.ova_sigmoid * sc[k]));
         if (!raw && m.softmax) {   // Common::Softmax
           double wmax = sc[0];
           for (int k = 1; k < K; ++k) wmax = std::max(sc[k], wmax);

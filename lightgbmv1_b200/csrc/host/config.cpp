@@ -110,6 +110,7 @@ std::string ObjectiveAlias(std::string t) {
       t == "l2_root" || t == "root_mean_squared_error" || t == "rmse") return "regression";
   if (t == "none" || t == "null" || t == "custom" || t == "na") return "custom";
   if (t == "multiclass" || t == "softmax") return "multiclass";
+  if (t == "multiclassova" || t == "multiclass_ova" || t == "ova" || t == "ovr") return "multiclassova";
   if (t == "regression_l1" || t == "mean_absolute_error" || t == "l1" || t == "mae") return "regression_l1";
   return t;
 }
@@ -266,7 +267,7 @@ void Config::Set(const std::unordered_map<std::string, std::string>& p) {
   if (min_gain_to_split < 0) Log::Fatal("min_gain_to_split should be >= 0");
   if (bin_construct_sample_cnt <= 0) Log::Fatal("bin_construct_sample_cnt should be > 0");
   // CheckParamConflict (src/io/config.cpp:249-273): objective, metric and num_class must agree
-  if (objective == "multiclass") {
+  if (objective == "multiclass" || objective == "multiclassova") {
     if (num_class <= 1) Log::Fatal("Number of classes should be specified and greater than 1 for multiclass training");
   } else {
     if (num_class != 1) Log::Fatal("Number of classes must be 1 for non-multiclass training");

@@ -3,6 +3,7 @@
 #include <algorithm>
 #include <cmath>
 #include <functional>
+#include <memory>
 #include <sstream>
 #include <vector>
 
@@ -16,7 +17,8 @@ void Check(int rc) {
 // src/objective/binary_objective.hpp
 class BinaryLogloss : public Objective {
  public:
-  explicit BinaryLogloss(const Config& c) : sigmoid_(c.sigmoid), is_unbalance_(c.is_unbalance), scale_pos_weight_(c.scale_pos_weight) {
+  // pos_class < 0: a row is positive when label > 0; otherwise when (int)label == pos_class (MulticlassOVA)
+  explicit BinaryLogloss(const Config& c, int pos_class = -1) : sigmoid_(c.sigmoid), is_unbalance_(c.is_unbalance), scale_pos_weight_(c.scale_pos_weight), pos_class_(pos_class) {
     if (sigmoid_ <= 0.0) Log::Fatal("Sigmoid parameter %f should be greater than zero", sigmoid_);
     if (is_unbalance_ && std::fabs(scale_pos_weight_ - 1.0f) > 1e-6) Log::Fatal("Cannot set is_unbalance and scale_pos_weight at the same time");
   }
@@ -26,7 +28,7 @@ class BinaryLogloss : public Objective {
     if (meta.label.empty()) Log::Fatal("Label should not be NULL");
     long long pos = 0, neg = 0;
 #pragma omp parallel for schedule(static) reduction(+:pos, neg)
-    for (data_size_t i = 0; i < n; ++i) { if (label_[i] > 0) ++pos; else ++neg; }
+    for (data_size_t i = 0; i < n; ++i) { if (IsPos(label_[i])) ++pos; else ++neg; }
     num_pos_ = static_cast<data_size_t>(pos);
     {  // binary_objective.hpp:72-75: the class counts of ALL machines decide need_train_ and the label weights
       double cnt[2] = {static_cast<double>(pos), static_cast<double>(neg)};  // counts < 2^53: exact as doubles
@@ -50,7 +52,7 @@ class BinaryLogloss : public Objective {
     double suml = 0.0f, sumw = 0.0f;
     if (weights_) {  // (the reference reduces over OpenMP threads too: binary_objective.hpp BoostFromScore)
 #pragma omp parallel for schedule(static) reduction(+:suml, sumw)
-      for (data_size_t i = 0; i < num_data_; ++i) { suml += (label_[i] > 0) * weights_[i]; sumw += weights_[i]; }
+      for (data_size_t i = 0; i < num_data_; ++i) { suml += IsPos(label_[i]) * weights_[i]; sumw += weights_[i]; }
     } else {
       sumw = static_cast<double>(num_data_);
       suml = static_cast<double>(num_pos_);  // a count: exact in any order
@@ -63,12 +65,14 @@ class BinaryLogloss : public Objective {
     return init;
   }
   bool NeedTrain(int) const override { return need_train_; }
+  double label_weight(int pos) const { return label_weights_[pos]; }
   void ConvertOutput(const double* in, double* out) const override { out[0] = 1.0f / (1.0f + std::exp(-sigmoid_ * in[0])); }
   std::string ToString() const override { std::ostringstream o; o << "binary sigmoid:" << sigmoid_; return o.str(); }
   const char* Name() const override { return "binary"; }
 
  private:
-  double sigmoid_; bool is_unbalance_; double scale_pos_weight_;
+  bool IsPos(label_t l) const { return pos_class_ < 0 ? l > 0 : static_cast<int>(l) == pos_class_; }
+  double sigmoid_; bool is_unbalance_; double scale_pos_weight_; int pos_class_;
   data_size_t num_data_ = 0, num_pos_ = 0; const label_t* label_ = nullptr; const label_t* weights_ = nullptr;
   bool need_train_ = true; double label_weights_[2] = {1, 1};
 };
@@ -246,15 +250,45 @@ class MulticlassSoftmax : public Objective {
   std::vector<double> class_init_probs_;
 };
 
+// src/objective/multiclass_objective.hpp:186-276 (MulticlassOVA): one BinaryLogloss per class
+class MulticlassOVA : public Objective {
+ public:
+  explicit MulticlassOVA(const Config& c) : num_class_(c.num_class), sigmoid_(c.sigmoid) {
+    for (int k = 0; k < num_class_; ++k) binary_.emplace_back(new BinaryLogloss(c, k));
+  }
+  void Init(const Metadata& meta, data_size_t n, const SumSync& sum_over_ranks) override {
+    for (auto& b : binary_) b->Init(meta, n, sum_over_ranks);
+  }
+  void Configure(LgbCuContext* ctx) const override {
+    Check(lgbcu_set_objective(ctx, LGBCU_OBJ_MULTICLASSOVA, num_class_, sigmoid_, 0));
+    std::vector<double> w;
+    for (auto& b : binary_) { w.push_back(b->label_weight(0)); w.push_back(b->label_weight(1)); }
+    Check(lgbcu_set_ova_label_weights(ctx, w.data(), num_class_));
+  }
+  double BoostFromScore(int k) const override { return binary_[k]->BoostFromScore(0); }
+  bool NeedTrain(int k) const override { return binary_[k]->NeedTrain(0); }
+  int NumModelPerIteration() const override { return num_class_; }
+  void ConvertOutput(const double* in, double* out) const override {
+    for (int i = 0; i < num_class_; ++i) out[i] = 1.0f / (1.0f + std::exp(-sigmoid_ * in[i]));
+  }
+  std::string ToString() const override { std::ostringstream o; o << "multiclassova num_class:" << num_class_ << " sigmoid:" << sigmoid_; return o.str(); }
+  const char* Name() const override { return "multiclassova"; }
+
+ private:
+  int num_class_; double sigmoid_;
+  std::vector<std::unique_ptr<BinaryLogloss>> binary_;
+};
+
 Objective* Objective::Create(const Config& c) {
   if (c.objective == "multiclass") return new MulticlassSoftmax(c);
+  if (c.objective == "multiclassova") return new MulticlassOVA(c);
   if (c.objective == "regression_l1") return new RegressionPercentile(c, false);
   if (c.objective == "quantile") return new RegressionPercentile(c, true);
   if (c.objective == "binary") return new BinaryLogloss(c);
   if (c.objective == "regression") return new RegressionL2(c);
   if (c.objective == "lambdarank") return new Lambdarank(c);
   if (c.objective == "custom") return nullptr;
-  Log::Fatal("objective=%s is outside this library's path (binary, regression/l2, regression_l1, quantile, lambdarank, multiclass, custom)", c.objective.c_str());
+  Log::Fatal("objective=%s is outside this library's path (binary, regression/l2, regression_l1, quantile, lambdarank, multiclass, multiclassova, custom)", c.objective.c_str());
 }
 
 }  // namespace lgb

@@ -25,12 +25,15 @@ def make(n, K, seed, F=10):
     return X, y
 
 
-@pytest.mark.parametrize("K,n,weighted", [(3, 30_000, False), (5, 20_000, True), (4, 12_000, False)])
-def test_multiclass_identical_trees_scores_metrics_predictions(K, n, weighted):
+@pytest.mark.parametrize("K,n,weighted,objective", [(3, 30_000, False, "multiclass"), (5, 20_000, True, "multiclass"),
+                                                    (4, 12_000, False, "multiclass"),
+                                                    # one-vs-all (multiclass_objective.hpp:186-276): a binary logloss per class, sigmoid outputs
+                                                    (3, 20_000, False, "multiclassova"), (4, 15_000, True, "multiclassova is_unbalance=true sigmoid=1.5")])
+def test_multiclass_identical_trees_scores_metrics_predictions(K, n, weighted, objective):
     X, y = make(n, K, 100 + K)
     w = (np.random.default_rng(1).random(n).astype(np.float32) + 0.5) if weighted else None
     Xv, yv = make(4000, K, 200 + K)
-    params = (f"objective=multiclass num_class={K} num_leaves=15 learning_rate=0.2 min_data_in_leaf=20 "
+    params = (f"objective={objective} num_class={K} num_leaves=15 learning_rate=0.2 min_data_in_leaf=20 "
               f"metric=multi_logloss,multi_error verbosity=-1 num_threads=4")
     out = []
     for lib, extra in ((capi.reference(), REF_EXTRA), (capi.ours(), "")):
@@ -64,7 +67,8 @@ def test_multiclass_identical_trees_scores_metrics_predictions(K, n, weighted):
     np.testing.assert_allclose(pvo, pvr, rtol=0, atol=1e-9)
     np.testing.assert_allclose(mo, mr, rtol=0, atol=1e-9)       # [row][class] from raw features
     np.testing.assert_allclose(ro, rr, rtol=0, atol=1e-9)
-    assert abs(po.reshape(K, n).sum(axis=0) - 1.0).max() < 1e-12
+    if objective == "multiclass":
+        assert abs(po.reshape(K, n).sum(axis=0) - 1.0).max() < 1e-12
     # rolling the last iteration back removes K trees and their scores in both libraries
     for lib, b in ((ref, br), (ours, bo)):
         lib.check(lib.lib.LGBM_BoosterRollbackOneIter(b))
