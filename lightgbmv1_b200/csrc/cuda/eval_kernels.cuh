@@ -45,6 +45,17 @@ __global__ void __launch_bounds__(EVAL_THREADS) k_eval_pointwise(int n, int kind
       loss = (s - y) * (s - y);
     } else if (kind == 2) {          // L1Metric::LossOnPoint (regression_metric.hpp:177)
       loss = fabs(s - y);
+    } else if (kind == 4) {          // HuberLossMetric::LossOnPoint (:191-198); `sigmoid` carries config.alpha
+      const double diff = s - y;
+      loss = fabs(diff) <= sigmoid ? 0.5f * diff * diff : sigmoid * (fabs(diff) - 0.5f * sigmoid);
+    } else if (kind == 5) {          // FairLossMetric::LossOnPoint (:212-216); `sigmoid` carries config.fair_c
+      const double x = fabs(s - y);
+      loss = sigmoid * x - sigmoid * sigmoid * log(1.0f + x / sigmoid);
+    } else if (kind == 6) {          // PoissonMetric::LossOnPoint (:229-235); `sigmoid` > 0: the objective's exp first
+      double t = sigmoid > 0.0 ? exp(s) : s;
+      const double eps = 1e-10f;
+      if (t < eps) t = eps;
+      loss = t - y * log(t);
     } else if (kind == 3) {          // QuantileMetric::LossOnPoint (:157-164); `sigmoid` carries config.alpha
       const double delta = y - s;
       loss = delta < 0 ? (sigmoid - 1.0f) * delta : sigmoid * delta;

@@ -39,6 +39,34 @@ __global__ void k_grad_l2(int n, const double* __restrict__ score, const float* 
   }
 }
 
+// RegressionHuberLoss (regression_objective.hpp:310-335; p0 = alpha), RegressionFairLoss (:363-380; p0 = c),
+// RegressionPoissonLoss (:441-457; p0 = max_delta_step): one pointwise kernel, kind = LGBCU_OBJ_*
+__global__ void k_grad_regression(int n, int kind, double p0, const double* __restrict__ score, const float* __restrict__ label,
+                                  const float* __restrict__ weight, float* __restrict__ grad, float* __restrict__ hess) {
+  for (int i = blockIdx.x * blockDim.x + threadIdx.x; i < n; i += gridDim.x * blockDim.x) {
+    double g, h;
+    if (kind == LGBCU_OBJ_HUBER) {
+      const double diff = score[i] - label[i];
+      if (fabs(diff) <= p0) g = diff; else g = ((diff > 0.0) - (diff < 0.0)) * p0;
+      if (weight == nullptr) { grad[i] = (float)g; hess[i] = 1.0f; }
+      else {
+        grad[i] = fabs(diff) <= p0 ? (float)(diff * weight[i]) : (float)(((diff > 0.0) - (diff < 0.0)) * weight[i] * p0);
+        hess[i] = (float)(weight[i]);
+      }
+      continue;
+    } else if (kind == LGBCU_OBJ_FAIR) {
+      const double x = score[i] - label[i];
+      g = p0 * x / (fabs(x) + p0);
+      h = p0 * p0 / ((fabs(x) + p0) * (fabs(x) + p0));
+    } else {  // poisson
+      g = exp(score[i]) - label[i];
+      h = exp(score[i] + p0);
+    }
+    if (weight == nullptr) { grad[i] = (float)g; hess[i] = (float)h; }
+    else { grad[i] = (float)(g * weight[i]); hess[i] = (float)(h * weight[i]); }
+  }
+}
+
 // RegressionL1loss::GetGradients (src/objective/regression_objective.hpp:214-231): sign(score - label) [* w], hessian 1 [w]
 __global__ void k_grad_l1(int n, const double* __restrict__ score, const float* __restrict__ label,
                           const float* __restrict__ weight, float* __restrict__ grad, float* __restrict__ hess) {

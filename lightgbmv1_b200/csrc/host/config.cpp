@@ -244,6 +244,10 @@ void Config::Set(const std::unordered_map<std::string, std::string>& p) {
   GetBool(p, "enable_bundle", &enable_bundle);
   GetDouble(p, "sigmoid", &sigmoid);
   GetDouble(p, "alpha", &alpha);
+  GetDouble(p, "fair_c", &fair_c);
+  GetDouble(p, "poisson_max_delta_step", &poisson_max_delta_step);
+  if (fair_c <= 0.0) Log::Fatal("fair_c should be > 0");
+  if (poisson_max_delta_step <= 0.0) Log::Fatal("poisson_max_delta_step should be > 0");
   if (alpha <= 0.0) Log::Fatal("alpha should be > 0");
   GetBool(p, "is_unbalance", &is_unbalance);
   GetDouble(p, "scale_pos_weight", &scale_pos_weight);

@@ -55,7 +55,8 @@ struct Config {
   bool enable_bundle = true;
   // objective
   double sigmoid = 1.0;
-  double alpha = 0.9;   // quantile objective / metric (config.h:815)
+  double alpha = 0.9;   // huber / quantile objectives and metrics (config.h:815)
+  double fair_c = 1.0, poisson_max_delta_step = 0.7;
   bool is_unbalance = false;
   double scale_pos_weight = 1.0;
   bool boost_from_average = true;

@@ -40,3 +40,23 @@ def test_percentile_objectives_identical_trees_and_leaf_values(objective, extra,
     for k in range(len(ref.eval_names(br))):
         np.testing.assert_allclose(ours.get_eval(bo, 0)[k], ref.get_eval(br, 0)[k], rtol=1e-9)
     assert ours.eval_names(bo) == ref.eval_names(br) == ["l1" if objective == "regression_l1" else "quantile"]
+
+
+@pytest.mark.parametrize("objective,weighted", [("huber alpha=1.2", False), ("huber", True), ("fair fair_c=0.8", False),
+                                                ("fair", True), ("poisson", False), ("poisson poisson_max_delta_step=0.5", True)])
+def test_pointwise_regression_objectives_identical_trees(objective, weighted):
+    """RegressionHuberLoss / RegressionFairLoss / RegressionPoissonLoss (regression_objective.hpp:290-477): pointwise
+    gradients on the device, the objective's own metric (through its ConvertOutput: exp for poisson) on the device."""
+    X, y = make(30_000, 11)
+    name = objective.split()[0]
+    if name == "poisson":
+        rng = np.random.default_rng(3)
+        y = rng.poisson(np.exp(0.4 * X[:, 0] + 0.2 * X[:, 1] + 0.5)).astype(np.float32)
+    w = (np.random.default_rng(4).random(len(y)).astype(np.float32) + 0.5) if weighted else None
+    params = f"objective={objective} num_leaves=31 learning_rate=0.1 min_data_in_leaf=20 verbosity=-1 num_threads=4"
+    ref, ours, br, bo, nr, no = run_both(X, y, params, 10, weight=w)
+    assert nr == no == 10
+    assert_same_model(ref, ours, br, bo)
+    np.testing.assert_allclose(ours.get_predict(bo, len(y)), ref.get_predict(br, len(y)), rtol=1e-9, atol=1e-9)
+    assert ours.eval_names(bo) == ref.eval_names(br) == [name]
+    np.testing.assert_allclose(ours.get_eval(bo, 0), ref.get_eval(br, 0), rtol=1e-9)
