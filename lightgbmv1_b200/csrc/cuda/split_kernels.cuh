@@ -501,7 +501,8 @@ struct FindTarget {
 //   * pull + reduce: entry by entry, pool[slot] = sum over the ranks' pool_local[slot], the peers' read over NVLink
 //     with system-scope loads.  64-bit integers: exact, the same on every rank.
 // The last block to finish records the epoch.  The split search afterwards reads `pool` exactly as it does on one GPU.
-#define XCHG_TIMEOUT_CYCLES 6000000000ll   /* ~3 s */
+#define XCHG_TIMEOUT_CYCLES 40000000000ll   /* ~20 s: a peer may be held up on its host (first-iteration set-up, a page-fault storm); once a wait has
+                                               timed out the error is sticky and later launches return at once */
 #define XCHG_THREADS 256
 struct XchgPeers { unsigned long long* flags[LGB_MAX_PEERS]; };   // rank r's flag array as mapped here
 // publish this rank's epoch `need` (block 0) and wait until every rank has reached it (every block)
@@ -541,7 +542,7 @@ __device__ __forceinline__ void xchg_finish(const DevView& V, unsigned long long
 //           half instead of N - 1 slots in the one-step form.
 __global__ void __launch_bounds__(XCHG_THREADS) k_xchg_pull(DevView V, XchgPeers P, int step) {
   DevCtl* c = V.ctl;
-  if (c->done) return;
+  if (c->done || c->xchg_error) return;
   const bool root_round = c->round == 0;
   if (root_round && c->skip_find) return;
   const unsigned long long need = c->xchg_epoch + 1;
