@@ -89,3 +89,17 @@ def test_multiclass_needs_num_class_and_matching_metric():
     with pytest.raises(Exception, match=r"Label must be in \[0, 3\)"):
         ours.booster_create(ds, "objective=multiclass num_class=3 verbosity=-1")
     ours.dataset_free(ds)
+
+
+def test_multiclass_with_bagging_and_column_sampling():
+    """one bag per iteration shared by the iteration's K trees (GBDT::Bagging runs once per TrainOneIter), one column
+    sample per tree (ColSampler::ResetByTree in every BeforeTrain): 3 x 10 trees identical to the reference's"""
+    K, n = 3, 25_000
+    X, y = make(n, K, 77)
+    params = (f"objective=multiclass num_class={K} num_leaves=15 learning_rate=0.1 min_data_in_leaf=10 verbosity=-1 num_threads=4 "
+              "bagging_fraction=0.7 bagging_freq=2 bagging_seed=3 feature_fraction=0.6 feature_fraction_seed=4")
+    from test_e2e_gpu import run_both
+    ref, ours, br, bo, nr, no = run_both(X, y, params, 10)
+    assert nr == no == 10
+    assert_same_model(ref, ours, br, bo)
+    np.testing.assert_allclose(ours.get_predict(bo, n * K), ref.get_predict(br, n * K), rtol=0, atol=1e-9)
