@@ -45,7 +45,8 @@ enum { LGBCU_MISSING_NONE = 0, LGBCU_MISSING_ZERO = 1, LGBCU_MISSING_NAN = 2 };
 /* objective kinds implemented on device (src/objective/) */
 enum { LGBCU_OBJ_NONE = 0, LGBCU_OBJ_BINARY = 1, LGBCU_OBJ_L2 = 2, LGBCU_OBJ_LAMBDARANK = 3, LGBCU_OBJ_MULTICLASS = 4,
        LGBCU_OBJ_L1 = 5, LGBCU_OBJ_QUANTILE = 6, LGBCU_OBJ_MULTICLASSOVA = 7,
-       LGBCU_OBJ_HUBER = 8 /* p0 = alpha */, LGBCU_OBJ_FAIR = 9 /* p0 = fair_c */, LGBCU_OBJ_POISSON = 10 /* p0 = poisson_max_delta_step */ };
+       LGBCU_OBJ_HUBER = 8 /* p0 = alpha */, LGBCU_OBJ_FAIR = 9 /* p0 = fair_c */, LGBCU_OBJ_POISSON = 10 /* p0 = poisson_max_delta_step */,
+       LGBCU_OBJ_GAMMA = 11, LGBCU_OBJ_TWEEDIE = 12 /* p0 = tweedie_variance_power */ };
 /* histogram kernel selection (LGBCU_HIST_AUTO picks by leaf size) */
 enum { LGBCU_HIST_AUTO = 0, LGBCU_HIST_GLOBAL_ATOMIC = 1, LGBCU_HIST_WARP_PRIVATE = 2 };
 
@@ -340,7 +341,9 @@ LGBCU_API int lgbcu_valid_copy_score(LgbCuContext* ctx, int32_t set, double* out
 #define LGBCU_METRIC_QUANTILE 8        /* `sigmoid` = alpha */
 #define LGBCU_METRIC_HUBER 9           /* `sigmoid` = alpha */
 #define LGBCU_METRIC_FAIR 10           /* `sigmoid` = fair_c */
-#define LGBCU_METRIC_POISSON 11        /* `sigmoid` > 0: exp(score) first (the poisson objective's ConvertOutput) */
+#define LGBCU_METRIC_POISSON 11        /* poisson / gamma / tweedie see exp(score) when the objective is one of the log-link ones */
+#define LGBCU_METRIC_GAMMA 12
+#define LGBCU_METRIC_TWEEDIE 13        /* `sigmoid` = tweedie_variance_power */
 LGBCU_API int lgbcu_eval_set_ndcg(LgbCuContext* ctx, int32_t set, const int32_t* eval_at, int32_t num_eval,
                                   const double* inv_max_dcg, const float* query_weight, const double* label_gain,
                                   int32_t num_label_gain, const double* discount, int32_t num_discount);

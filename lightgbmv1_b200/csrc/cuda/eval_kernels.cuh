@@ -32,7 +32,8 @@ __device__ __forceinline__ double block_sum_f64(double v, double* s_warp) {
 
 // kind 0: (score - label)^2 [* w]   (RegressionMetric<L2Metric>::LossOnPoint)
 // kind 1: binary logloss of prob = 1 / (1 + exp(-sigmoid * score))   (BinaryLoglossMetric::LossOnPoint, kEpsilon clip)
-__global__ void __launch_bounds__(EVAL_THREADS) k_eval_pointwise(int n, int kind, double sigmoid, const double* __restrict__ score,
+__device__ __forceinline__ double safe_log(double x) { return x > 0 ? log(x) : -INFINITY; }   // Common::SafeLog
+__global__ void __launch_bounds__(EVAL_THREADS) k_eval_pointwise(int n, int kind, double sigmoid, int conv_exp, const double* __restrict__ score,
                                                                  const float* __restrict__ label, const float* __restrict__ weight,
                                                                  double* __restrict__ partial) {
   __shared__ double s_warp[EVAL_THREADS / 32];
@@ -51,11 +52,26 @@ __global__ void __launch_bounds__(EVAL_THREADS) k_eval_pointwise(int n, int kind
     } else if (kind == 5) {          // FairLossMetric::LossOnPoint (:212-216); `sigmoid` carries config.fair_c
       const double x = fabs(s - y);
       loss = sigmoid * x - sigmoid * sigmoid * log(1.0f + x / sigmoid);
-    } else if (kind == 6) {          // PoissonMetric::LossOnPoint (:229-235); `sigmoid` > 0: the objective's exp first
-      double t = sigmoid > 0.0 ? exp(s) : s;
+    } else if (kind == 6) {          // PoissonMetric::LossOnPoint (:229-235); conv_exp: the objective's exp first
+      double t = conv_exp ? exp(s) : s;
       const double eps = 1e-10f;
       if (t < eps) t = eps;
       loss = t - y * log(t);
+    } else if (kind == 7) {          // GammaMetric::LossOnPoint (:261-268), written out as there (psi = 1)
+      const double t = conv_exp ? exp(s) : s;
+      const double psi = 1.0;
+      const double theta = -1.0 / t;
+      const double a = psi;
+      const double b = -safe_log(-theta);
+      const double c = 1. / psi * safe_log(y / psi) - safe_log(y) - 0;
+      loss = -((y * theta - b) / a + c);
+    } else if (kind == 8) {          // TweedieMetric::LossOnPoint (:305-314); `sigmoid` carries tweedie_variance_power
+      double t = conv_exp ? exp(s) : s;
+      const double eps = 1e-10f;
+      if (t < eps) t = eps;
+      const double a = y * exp((1 - sigmoid) * log(t)) / (1 - sigmoid);
+      const double b = exp((2 - sigmoid) * log(t)) / (2 - sigmoid);
+      loss = -a + b;
     } else if (kind == 3) {          // QuantileMetric::LossOnPoint (:157-164); `sigmoid` carries config.alpha
       const double delta = y - s;
       loss = delta < 0 ? (sigmoid - 1.0f) * delta : sigmoid * delta;

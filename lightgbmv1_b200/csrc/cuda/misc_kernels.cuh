@@ -58,6 +58,18 @@ __global__ void k_grad_regression(int n, int kind, double p0, const double* __re
       const double x = score[i] - label[i];
       g = p0 * x / (fabs(x) + p0);
       h = p0 * p0 / ((fabs(x) + p0) * (fabs(x) + p0));
+    } else if (kind == LGBCU_OBJ_GAMMA) {   // RegressionGammaLoss (:683-701); the weight multiplies the second term only
+      if (weight == nullptr) {
+        grad[i] = (float)(1.0 - label[i] / exp(score[i]));
+        hess[i] = (float)(label[i] / exp(score[i]));
+      } else {
+        grad[i] = (float)(1.0 - label[i] / exp(score[i]) * weight[i]);
+        hess[i] = (float)(label[i] / exp(score[i]) * weight[i]);
+      }
+      continue;
+    } else if (kind == LGBCU_OBJ_TWEEDIE) { // RegressionTweedieLoss (:720-738); p0 = tweedie_variance_power
+      g = -label[i] * exp((1 - p0) * score[i]) + exp((2 - p0) * score[i]);
+      h = -label[i] * (1 - p0) * exp((1 - p0) * score[i]) + (2 - p0) * exp((2 - p0) * score[i]);
     } else {  // poisson
       g = exp(score[i]) - label[i];
       h = exp(score[i] + p0);

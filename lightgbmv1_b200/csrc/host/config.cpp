@@ -246,6 +246,8 @@ void Config::Set(const std::unordered_map<std::string, std::string>& p) {
   GetDouble(p, "alpha", &alpha);
   GetDouble(p, "fair_c", &fair_c);
   GetDouble(p, "poisson_max_delta_step", &poisson_max_delta_step);
+  GetDouble(p, "tweedie_variance_power", &tweedie_variance_power);
+  if (tweedie_variance_power < 1.0 || tweedie_variance_power >= 2.0) Log::Fatal("tweedie_variance_power should be in [1, 2)");
   if (fair_c <= 0.0) Log::Fatal("fair_c should be > 0");
   if (poisson_max_delta_step <= 0.0) Log::Fatal("poisson_max_delta_step should be > 0");
   if (alpha <= 0.0) Log::Fatal("alpha should be > 0");

@@ -56,7 +56,7 @@ struct Config {
   // objective
   double sigmoid = 1.0;
   double alpha = 0.9;   // huber / quantile objectives and metrics (config.h:815)
-  double fair_c = 1.0, poisson_max_delta_step = 0.7;
+  double fair_c = 1.0, poisson_max_delta_step = 0.7, tweedie_variance_power = 1.5;
   bool is_unbalance = false;
   double scale_pos_weight = 1.0;
   bool boost_from_average = true;

@@ -122,6 +122,8 @@ GBDT::GBDT(const Dataset* train, const Config& config)
     else if (m == "huber") { spec.kind = LGBCU_METRIC_HUBER; spec.names = {"huber"}; }
     else if (m == "fair") { spec.kind = LGBCU_METRIC_FAIR; spec.names = {"fair"}; }
     else if (m == "poisson") { spec.kind = LGBCU_METRIC_POISSON; spec.names = {"poisson"}; }
+    else if (m == "gamma") { spec.kind = LGBCU_METRIC_GAMMA; spec.names = {"gamma"}; }
+    else if (m == "tweedie") { spec.kind = LGBCU_METRIC_TWEEDIE; spec.names = {"tweedie"}; }
     else if (m == "quantile") { spec.kind = LGBCU_METRIC_QUANTILE; spec.names = {"quantile"}; }
     else if (m == "multi_logloss") { spec.kind = LGBCU_METRIC_MULTI_LOGLOSS; spec.names = {"multi_logloss"}; }
     else if (m == "multi_error") {
@@ -129,7 +131,7 @@ GBDT::GBDT(const Dataset* train, const Config& config)
       spec.names = {config_.multi_error_top_k == 1 ? std::string("multi_error") : "multi_error@" + std::to_string(config_.multi_error_top_k)};
     }
     else if (m == "custom") continue;
-    else Log::Fatal("metric=%s is outside this library's path (l2, rmse, l1, huber, fair, poisson, quantile, binary_logloss, auc, ndcg, multi_logloss, multi_error)", m.c_str());
+    else Log::Fatal("metric=%s is outside this library's path (l2, rmse, l1, huber, fair, poisson, gamma, tweedie, quantile, binary_logloss, auc, ndcg, multi_logloss, multi_error)", m.c_str());
     if ((spec.kind == LGBCU_METRIC_MULTI_LOGLOSS || spec.kind == LGBCU_METRIC_MULTI_ERROR) != (num_tree_per_iteration_ > 1))
       Log::Fatal("Multiclass objective and metrics don't match");
     metrics_.push_back(spec);
@@ -524,7 +526,7 @@ std::vector<double> GBDT::GetEvalAt(int data_idx) {
     double sig = (objective_ && std::string(objective_->Name()) == "binary") ? config_.sigmoid : 0.0;
     if (m.kind == LGBCU_METRIC_QUANTILE || m.kind == LGBCU_METRIC_HUBER) sig = config_.alpha;
     if (m.kind == LGBCU_METRIC_FAIR) sig = config_.fair_c;
-    if (m.kind == LGBCU_METRIC_POISSON) sig = (objective_ && std::string(objective_->Name()) == "poisson") ? 1.0 : 0.0;
+    if (m.kind == LGBCU_METRIC_TWEEDIE) sig = config_.tweedie_variance_power;
     if (m.kind == LGBCU_METRIC_MULTI_LOGLOSS) sig = objective_ ? 1.0 : 0.0;                                       // softmax first
     if (m.kind == LGBCU_METRIC_MULTI_ERROR) sig = (objective_ ? 1.0 : -1.0) * config_.multi_error_top_k;
     Check(lgbcu_eval(ctx_, set, m.kind, sig, buf, 64));

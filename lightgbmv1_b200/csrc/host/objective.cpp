@@ -258,13 +258,14 @@ class RegressionPointwise : public Objective {
   RegressionPointwise(const Config& c, int kind) : kind_(kind) {
     if (kind_ == LGBCU_OBJ_HUBER) p0_ = static_cast<double>(c.alpha);
     else if (kind_ == LGBCU_OBJ_FAIR) p0_ = static_cast<double>(c.fair_c);
+    else if (kind_ == LGBCU_OBJ_TWEEDIE) p0_ = c.tweedie_variance_power;
     else p0_ = static_cast<double>(c.poisson_max_delta_step);
     if (c.reg_sqrt) Log::Warning("Cannot use sqrt transform in %s Regression, will auto disable it", Name());
   }
   void Init(const Metadata& meta, data_size_t n, const SumSync&) override {
     num_data_ = n; label_ = meta.label.data(); weights_ = meta.weights.empty() ? nullptr : meta.weights.data();
     if (meta.label.empty()) Log::Fatal("Label should not be NULL");
-    if (kind_ == LGBCU_OBJ_POISSON) {
+    if (LogLink()) {   // RegressionPoissonLoss::Init, inherited by gamma and tweedie
       label_t miny = label_[0]; double sumy = 0.0;
       for (data_size_t i = 0; i < n; ++i) { miny = std::min(miny, label_[i]); sumy += label_[i]; }
       if (miny < 0.0f) Log::Fatal("[%s]: at least one target label is negative", Name());
@@ -283,14 +284,18 @@ class RegressionPointwise : public Objective {
       for (data_size_t i = 0; i < num_data_; ++i) suml += label_[i];
     }
     const double mean = suml / sumw;
-    if (kind_ == LGBCU_OBJ_POISSON) return mean > 0 ? std::log(mean) : -std::numeric_limits<double>::infinity();  // Common::SafeLog
+    if (LogLink()) return mean > 0 ? std::log(mean) : -std::numeric_limits<double>::infinity();  // Common::SafeLog
     return mean;
   }
-  void ConvertOutput(const double* in, double* out) const override { out[0] = kind_ == LGBCU_OBJ_POISSON ? std::exp(in[0]) : in[0]; }
+  void ConvertOutput(const double* in, double* out) const override { out[0] = LogLink() ? std::exp(in[0]) : in[0]; }
   std::string ToString() const override { return Name(); }
-  const char* Name() const override { return kind_ == LGBCU_OBJ_HUBER ? "huber" : kind_ == LGBCU_OBJ_FAIR ? "fair" : "poisson"; }
+  const char* Name() const override {
+    return kind_ == LGBCU_OBJ_HUBER ? "huber" : kind_ == LGBCU_OBJ_FAIR ? "fair" : kind_ == LGBCU_OBJ_GAMMA ? "gamma" :
+           kind_ == LGBCU_OBJ_TWEEDIE ? "tweedie" : "poisson";
+  }
 
  private:
+  bool LogLink() const { return kind_ == LGBCU_OBJ_POISSON || kind_ == LGBCU_OBJ_GAMMA || kind_ == LGBCU_OBJ_TWEEDIE; }
   int kind_; double p0_ = 0.0;
   data_size_t num_data_ = 0; const label_t* label_ = nullptr; const label_t* weights_ = nullptr;
 };
@@ -330,13 +335,15 @@ Objective* Objective::Create(const Config& c) {
   if (c.objective == "huber") return new RegressionPointwise(c, LGBCU_OBJ_HUBER);
   if (c.objective == "fair") return new RegressionPointwise(c, LGBCU_OBJ_FAIR);
   if (c.objective == "poisson") return new RegressionPointwise(c, LGBCU_OBJ_POISSON);
+  if (c.objective == "gamma") return new RegressionPointwise(c, LGBCU_OBJ_GAMMA);
+  if (c.objective == "tweedie") return new RegressionPointwise(c, LGBCU_OBJ_TWEEDIE);
   if (c.objective == "regression_l1") return new RegressionPercentile(c, false);
   if (c.objective == "quantile") return new RegressionPercentile(c, true);
   if (c.objective == "binary") return new BinaryLogloss(c);
   if (c.objective == "regression") return new RegressionL2(c);
   if (c.objective == "lambdarank") return new Lambdarank(c);
   if (c.objective == "custom") return nullptr;
-  Log::Fatal("objective=%s is outside this library's path (binary, regression/l2, regression_l1, huber, fair, poisson, quantile, lambdarank, multiclass, multiclassova, custom)", c.objective.c_str());
+  Log::Fatal("objective=%s is outside this library's path (binary, regression/l2, regression_l1, huber, fair, poisson, gamma, tweedie, quantile, lambdarank, multiclass, multiclassova, custom)", c.objective.c_str());
 }
 
 }  // namespace lgb

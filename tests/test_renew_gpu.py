@@ -43,15 +43,20 @@ def test_percentile_objectives_identical_trees_and_leaf_values(objective, extra,
 
 
 @pytest.mark.parametrize("objective,weighted", [("huber alpha=1.2", False), ("huber", True), ("fair fair_c=0.8", False),
-                                                ("fair", True), ("poisson", False), ("poisson poisson_max_delta_step=0.5", True)])
+                                                ("fair", True), ("poisson", False), ("poisson poisson_max_delta_step=0.5", True),
+                                                ("gamma", False), ("gamma", True), ("tweedie", False),
+                                                ("tweedie tweedie_variance_power=1.2", True)])
 def test_pointwise_regression_objectives_identical_trees(objective, weighted):
-    """RegressionHuberLoss / RegressionFairLoss / RegressionPoissonLoss (regression_objective.hpp:290-477): pointwise
+    """RegressionHuberLoss / FairLoss / PoissonLoss / GammaLoss / TweedieLoss (regression_objective.hpp:290-477, 672-748): pointwise
     gradients on the device, the objective's own metric (through its ConvertOutput: exp for poisson) on the device."""
     X, y = make(30_000, 11)
     name = objective.split()[0]
-    if name == "poisson":
+    if name in ("poisson", "tweedie"):
         rng = np.random.default_rng(3)
         y = rng.poisson(np.exp(0.4 * X[:, 0] + 0.2 * X[:, 1] + 0.5)).astype(np.float32)
+    if name == "gamma":   # strictly positive targets
+        rng = np.random.default_rng(3)
+        y = rng.gamma(2.0, np.exp(0.3 * X[:, 0] - 0.2 * X[:, 1]) / 2.0).astype(np.float32) + 1e-3
     w = (np.random.default_rng(4).random(len(y)).astype(np.float32) + 0.5) if weighted else None
     params = f"objective={objective} num_leaves=31 learning_rate=0.1 min_data_in_leaf=20 verbosity=-1 num_threads=4"
     ref, ours, br, bo, nr, no = run_both(X, y, params, 10, weight=w)
