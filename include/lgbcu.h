@@ -344,6 +344,7 @@ LGBCU_API int lgbcu_valid_copy_score(LgbCuContext* ctx, int32_t set, double* out
 #define LGBCU_METRIC_POISSON 11        /* poisson / gamma / tweedie see exp(score) when the objective is one of the log-link ones */
 #define LGBCU_METRIC_GAMMA 12
 #define LGBCU_METRIC_TWEEDIE 13        /* `sigmoid` = tweedie_variance_power */
+#define LGBCU_METRIC_BINARY_ERROR 14   /* `sigmoid` as for binary_logloss */
 LGBCU_API int lgbcu_eval_set_ndcg(LgbCuContext* ctx, int32_t set, const int32_t* eval_at, int32_t num_eval,
                                   const double* inv_max_dcg, const float* query_weight, const double* label_gain,
                                   int32_t num_label_gain, const double* discount, int32_t num_discount);

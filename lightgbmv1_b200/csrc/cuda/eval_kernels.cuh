@@ -57,6 +57,9 @@ __global__ void __launch_bounds__(EVAL_THREADS) k_eval_pointwise(int n, int kind
       const double eps = 1e-10f;
       if (t < eps) t = eps;
       loss = t - y * log(t);
+    } else if (kind == 9) {          // BinaryErrorMetric::LossOnPoint (binary_metric.hpp:143-149) of the converted score
+      const double prob = sigmoid > 0.0 ? 1.0f / (1.0f + exp(-sigmoid * s)) : s;
+      loss = prob <= 0.5f ? (y > 0 ? 1.0 : 0.0) : (y <= 0 ? 1.0 : 0.0);
     } else if (kind == 7) {          // GammaMetric::LossOnPoint (:261-268), written out as there (psi = 1)
       const double t = conv_exp ? exp(s) : s;
       const double psi = 1.0;

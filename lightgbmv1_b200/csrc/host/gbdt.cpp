@@ -113,6 +113,7 @@ GBDT::GBDT(const Dataset* train, const Config& config)
     if (m == "l2") { spec.kind = LGBCU_METRIC_L2; spec.names = {"l2"}; }
     else if (m == "rmse") { spec.kind = LGBCU_METRIC_RMSE; spec.names = {"rmse"}; }
     else if (m == "binary_logloss") { spec.kind = LGBCU_METRIC_BINARY_LOGLOSS; spec.names = {"binary_logloss"}; }
+    else if (m == "binary_error") { spec.kind = LGBCU_METRIC_BINARY_ERROR; spec.names = {"binary_error"}; }
     else if (m == "auc") { spec.kind = LGBCU_METRIC_AUC; spec.names = {"auc"}; }
     else if (m == "ndcg") {
       spec.kind = LGBCU_METRIC_NDCG;
@@ -131,7 +132,7 @@ GBDT::GBDT(const Dataset* train, const Config& config)
       spec.names = {config_.multi_error_top_k == 1 ? std::string("multi_error") : "multi_error@" + std::to_string(config_.multi_error_top_k)};
     }
     else if (m == "custom") continue;
-    else Log::Fatal("metric=%s is outside this library's path (l2, rmse, l1, huber, fair, poisson, gamma, tweedie, quantile, binary_logloss, auc, ndcg, multi_logloss, multi_error)", m.c_str());
+    else Log::Fatal("metric=%s is outside this library's path (l2, rmse, l1, huber, fair, poisson, gamma, tweedie, quantile, binary_logloss, binary_error, auc, ndcg, multi_logloss, multi_error)", m.c_str());
     if ((spec.kind == LGBCU_METRIC_MULTI_LOGLOSS || spec.kind == LGBCU_METRIC_MULTI_ERROR) != (num_tree_per_iteration_ > 1))
       Log::Fatal("Multiclass objective and metrics don't match");
     metrics_.push_back(spec);

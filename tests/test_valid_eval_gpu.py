@@ -58,10 +58,10 @@ def test_binary_logloss_and_auc(weighted):
     rng = np.random.default_rng(5)
     wt = (rng.random(len(yt)) + 0.5).astype(np.float32) if weighted else None
     wv = (rng.random(len(yv)) + 0.5).astype(np.float32) if weighted else None
-    params = "objective=binary metric=binary_logloss,auc num_leaves=31 min_data_in_leaf=20 learning_rate=0.1 verbosity=-1"
+    params = "objective=binary metric=binary_logloss,auc,binary_error num_leaves=31 min_data_in_leaf=20 learning_rate=0.1 verbosity=-1"
     ref = _run(capi.reference(), Xt, yt, Xv, yv, params, 8, wt, wv, extra=REF_EXTRA)
     ours = _run(capi.ours(), Xt, yt, Xv, yv, params, 8, wt, wv)
-    assert ref[0] == ["binary_logloss", "auc"]
+    assert ref[0] == ["binary_logloss", "auc", "binary_error"]
     _compare(ref, ours)
 
 
