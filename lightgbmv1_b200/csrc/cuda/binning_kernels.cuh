@@ -9,14 +9,15 @@
 
 struct LgbCuBinnedMatrix {
   int device = 0; int32_t nrow = 0, nfeat = 0;
-  uint8_t* d_bins = nullptr;     // [nrow][nfeat] stored values, row-major, no padding
+  uint8_t* d_bins = nullptr;     // [nrow][nfeat] stored values, row-major, no padding; nfeat = BYTE columns: one per
+                                 // feature, two (low byte first) per feature with more than 256 stored values
 };
 
-struct BinFeatDev { int column, num_bin, mfb, missing_type, bound_off, pad; };
+struct BinFeatDev { int column, num_bin, mfb, missing_type, bound_off, scol; };   // scol = (first) byte column of the output
 
 template <typename T>
 __global__ void __launch_bounds__(256) k_bin_rows(const T* __restrict__ x, long long rows, int ncol, int row_major, long long ld,
-                                                  int F, const BinFeatDev* __restrict__ feats, const double* __restrict__ bounds,
+                                                  int F, int FS, const BinFeatDev* __restrict__ feats, const double* __restrict__ bounds,
                                                   uint8_t* __restrict__ out) {
   const long long total = rows * F;
   for (long long i = blockIdx.x * (long long)blockDim.x + threadIdx.x; i < total; i += (long long)gridDim.x * blockDim.x) {
@@ -40,7 +41,9 @@ __global__ void __launch_bounds__(256) k_bin_rows(const T* __restrict__ x, long 
     }
     int stored = 0;
     if (bin != d.mfb) stored = bin + (d.mfb == 0 ? 0 : 1);   // bin + 1 - [mfb == 0]
-    out[i] = (uint8_t)stored;
+    uint8_t* o = out + r * FS + d.scol;
+    o[0] = (uint8_t)(stored & 255);
+    if (d.num_bin + (d.mfb == 0 ? 0 : 1) > 256) o[1] = (uint8_t)(stored >> 8);   // a wide feature: two byte columns
   }
 }
 
@@ -113,14 +116,16 @@ int lgbcu_bin_matrix(int device, const void* data, int data_type, int32_t nrow, 
          feats[f].bound_offset + feats[f].num_bin <= num_bounds, "lgbcu_bin_matrix: bad descriptor of feature %d", f);
     hf[f] = BinFeatDev{feats[f].column, feats[f].num_bin, feats[f].most_freq_bin, feats[f].missing_type, feats[f].bound_offset, 0};
   }
+  int FS = 0;   // byte columns of the result
+  for (int f = 0; f < num_features; ++f) { hf[f].scol = FS; FS += (hf[f].num_bin + (hf[f].mfb == 0 ? 0 : 1) > 256) ? 2 : 1; }
   BinFeatDev* d_feats = nullptr; double* d_bounds = nullptr;
   CU(lgb_dev_malloc(&G.dev[0], sizeof(BinFeatDev) * num_features)); d_feats = static_cast<BinFeatDev*>(G.dev[0]);
   CU(lgb_dev_malloc(&G.dev[1], sizeof(double) * num_bounds)); d_bounds = static_cast<double*>(G.dev[1]);
   CU(cudaMemcpy(d_feats, hf.data(), sizeof(BinFeatDev) * num_features, cudaMemcpyHostToDevice));
   CU(cudaMemcpy(d_bounds, upper_bounds, sizeof(double) * num_bounds, cudaMemcpyHostToDevice));
   G.m = new LgbCuBinnedMatrix();
-  G.m->device = device; G.m->nrow = nrow; G.m->nfeat = num_features;
-  CU(lgb_dev_malloc(reinterpret_cast<void**>(&G.m->d_bins), (size_t)nrow * num_features));
+  G.m->device = device; G.m->nrow = nrow; G.m->nfeat = FS;
+  CU(lgb_dev_malloc(reinterpret_cast<void**>(&G.m->d_bins), (size_t)nrow * FS));
   for (int i = 0; i < 2; ++i) { CU(cudaStreamCreateWithFlags(&G.s[i], cudaStreamNonBlocking)); CU(cudaEventCreateWithFlags(&G.ev[i], cudaEventDisableTiming)); }
   tick("descriptors + result alloc");
   int sm_count = 0;
@@ -153,9 +158,9 @@ int lgbcu_bin_matrix(int device, const void* data, int data_type, int32_t nrow, 
       CU(cudaEventRecord(G.ev[b], G.s[b]));
       const long long work = (long long)rows * num_features;
       const int grid = (int)std::min<long long>(max_grid, (work + 255) / 256);
-      uint8_t* dst = G.m->d_bins + r0 * num_features;
-      if (data_type == 0) k_bin_rows<float><<<grid, 256, 0, G.s[b]>>>(static_cast<const float*>(G.dev[2 + b]), (long long)rows, ncol, 1, 0, num_features, d_feats, d_bounds, dst);
-      else k_bin_rows<double><<<grid, 256, 0, G.s[b]>>>(static_cast<const double*>(G.dev[2 + b]), (long long)rows, ncol, 1, 0, num_features, d_feats, d_bounds, dst);
+      uint8_t* dst = G.m->d_bins + r0 * FS;
+      if (data_type == 0) k_bin_rows<float><<<grid, 256, 0, G.s[b]>>>(static_cast<const float*>(G.dev[2 + b]), (long long)rows, ncol, 1, 0, num_features, FS, d_feats, d_bounds, dst);
+      else k_bin_rows<double><<<grid, 256, 0, G.s[b]>>>(static_cast<const double*>(G.dev[2 + b]), (long long)rows, ncol, 1, 0, num_features, FS, d_feats, d_bounds, dst);
       g_launches.fetch_add(1, std::memory_order_relaxed);
       CU(cudaGetLastError());
     }
@@ -172,8 +177,8 @@ int lgbcu_bin_matrix(int device, const void* data, int data_type, int32_t nrow, 
     CU(cudaMemcpyAsync(d_feats, hc.data(), sizeof(BinFeatDev) * num_features, cudaMemcpyHostToDevice, G.s[0]));
     const long long work = (long long)nrow * num_features;
     const int grid = (int)std::min<long long>(max_grid, (work + 255) / 256);
-    if (data_type == 0) k_bin_rows<float><<<grid, 256, 0, G.s[0]>>>(static_cast<const float*>(G.dev[2]), (long long)nrow, num_features, 0, (long long)nrow, num_features, d_feats, d_bounds, G.m->d_bins);
-    else k_bin_rows<double><<<grid, 256, 0, G.s[0]>>>(static_cast<const double*>(G.dev[2]), (long long)nrow, num_features, 0, (long long)nrow, num_features, d_feats, d_bounds, G.m->d_bins);
+    if (data_type == 0) k_bin_rows<float><<<grid, 256, 0, G.s[0]>>>(static_cast<const float*>(G.dev[2]), (long long)nrow, num_features, 0, (long long)nrow, num_features, FS, d_feats, d_bounds, G.m->d_bins);
+    else k_bin_rows<double><<<grid, 256, 0, G.s[0]>>>(static_cast<const double*>(G.dev[2]), (long long)nrow, num_features, 0, (long long)nrow, num_features, FS, d_feats, d_bounds, G.m->d_bins);
     g_launches.fetch_add(1, std::memory_order_relaxed);
     CU(cudaGetLastError());
   }
@@ -204,7 +209,11 @@ int lgbcu_set_dataset_binned(LgbCuContext* c, const LgbCuBinnedMatrix* m, const 
   NEED(c && m && meta, "lgbcu_set_dataset_binned: NULL argument");
   NEED(m->device == c->device, "lgbcu_set_dataset_binned: the matrix lives on device %d, the learner on device %d", m->device, c->device);
   USE_DEVICE(c->device);
-  if (setup_dataset_common(c, m->nrow, m->nfeat, meta)) return -1;
+  // (setup_dataset_common derives the byte columns from the metas; they must be the matrix's)
+  int fs = 0, nf = 0;
+  for (; fs < m->nfeat; ++nf) { const int ns = 1 + meta[nf].num_bin - (meta[nf].most_freq_bin == 0 ? 1 : 0); fs += ns > 256 ? 2 : 1; }
+  NEED(fs == m->nfeat, "lgbcu_set_dataset_binned: the feature descriptors do not match the matrix's %d byte columns", m->nfeat);
+  if (setup_dataset_common(c, m->nrow, nf, meta)) return -1;
   LAUNCH(k_pad_rows, grid_for(c, (long long)m->nrow * (c->stride / 4), 256), 256, 0, c->stream, (long long)m->nrow,
          m->nfeat, c->stride, m->d_bins, c->d_bins);
   LAUNCH(k_transpose_bins, grid_for(c, m->nrow, 256), 256, 0, c->stream, m->nrow, m->nfeat, c->stride, c->d_bins,

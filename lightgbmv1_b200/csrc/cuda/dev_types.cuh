@@ -25,8 +25,18 @@ struct DevFeat {
   int hist_base;     // first slot of the feature's (single-feature) group = group_bin_boundaries_[g]
   int nslots;        // FeatureGroup::num_total_bin_ = 1 + num_bin - offset
   int real_index;
+  // Storage: a feature with at most 256 stored values (nslots <= 256) is one byte column of the matrix; a WIDE feature
+  // (max_bin > 255: the reference's 16-bit DenseBin, src/io/bin.cpp:635-645) is two adjacent byte columns, low byte
+  // first.  `col` = the (first) byte column.  The matrices stay byte matrices, so the kernels of the 8-bit hot path are
+  // untouched; data with a wide feature takes the general histogram and split-search paths.
+  int col, wide;
   double penalty;
 };
+
+// stored value of feature F in a row-major row / in the column-major copy
+__device__ __forceinline__ int stored_bin_row(const uint8_t* __restrict__ row, const DevFeat& F) {
+  return F.wide ? (int)row[F.col] | ((int)row[F.col + 1] << 8) : (int)row[F.col];
+}
 
 struct DevSplit {    // SplitInfo, POD
   double gain;
@@ -128,6 +138,7 @@ struct DevParams {   // LgbCuTreeParams + derived switches
 // Everything the kernels need, passed by value (fits in the 4 KB parameter space with room to spare).
 struct DevView {
   int num_data, num_features, row_stride, total_bin, num_tiles16;
+  int num_storage, any_wide;   // byte columns of the matrices (= num_features unless a feature is wide)
   int data_parallel;         // 1: histograms are all-reduced across ranks, leaf counts are the global estimates
   int f_begin, f_end;        // features this rank scans in k_find_split: all of them, or its block in ownership mode
   int comm_size;             // ranks (ownership mode: rows of cand_all per (leaf, child))

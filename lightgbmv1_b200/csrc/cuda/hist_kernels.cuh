@@ -100,6 +100,27 @@ __device__ void hist_global_path(const DevView& V, const DevLeaf& L, bool identi
   }
 }
 
+// Data with a wide feature (more than 256 stored values: two byte columns, dev_types.cuh): one thread per (row, feature),
+// two REDG.ADD.64 per pair straight into the pool slot.  The general path -- any number of bins per feature -- and a slow
+// one (global atomics; the 8-bit sub-histogram path above it in hist_phase is what the benchmarks run).
+__device__ void hist_global_wide_path(const DevView& V, const DevLeaf& L, bool identity, int bid, int nblocks) {
+  const int* idx = V.indices[L.buf] + L.begin;
+  HistEntry* out = V.hist_pool + (size_t)L.slot * V.total_bin;
+  const int F = V.num_features;
+  const long long total = (long long)L.count * F;
+  for (long long p = bid * (long long)blockDim.x + threadIdx.x; p < total; p += (long long)nblocks * blockDim.x) {
+    const int pos = (int)(p / F);
+    const int f = (int)(p - (long long)pos * F);
+    const int row = identity ? pos : idx[pos];
+    const DevFeat Ft = V.feats[f];
+    const int b = stored_bin_row(V.bins + (size_t)row * V.row_stride, Ft);
+    const float2 gh = V.gh[row];
+    HistEntry* e = out + Ft.hist_base + b;
+    atomic_add_i64(&e->g, to_fixed(gh.x, V.ctl->scale_g));
+    atomic_add_i64(&e->h, to_fixed(gh.y, V.ctl->scale_h));
+  }
+}
+
 // One 64-bit add into a (low word, high word) pair of shared memory, in two steps so that the low-word adds of
 // several rows are in flight before any of their results is needed (an ATOMS result takes > 100 cycles to come back):
 //   hist_atom_lo: low += v_lo, returns the old low word.  `e` = 32-bit shared address of the low word.
@@ -285,28 +306,26 @@ __device__ void hist_phase(const DevView& V, const DevLeaf& L, bool is_root, int
 
 // leaf_arg >= 0: that leaf (step-wise API).  leaf_arg < 0: training -- round 0 builds the root, every later round the
 // smaller child of each leaf being expanded (DevSpec); all of a round's leaves share this one launch.
-__global__ void __cluster_dims__(HIST_CLUSTER, 1, 1) __launch_bounds__(HIST_THREADS, HIST_BLOCKS_PER_SM) k_hist(DevView V, int leaf_arg, int mode, int min_rows, int small_rows) {
-  extern __shared__ __align__(16) unsigned char hist_smem[];
+// Which leaf a block of the histogram launch works for, and as which block of how many (false: nothing to do).
+// leaf_arg >= 0: that leaf (step-wise API).  leaf_arg < 0: training -- round 0 builds the root, every later round the
+// smaller child of each leaf being expanded; all of a round's leaves share the launch.  `unit` = blocks that stay
+// together (a cluster).
+__device__ __forceinline__ bool hist_pick_work(const DevView& V, int leaf_arg, int unit, DevLeaf* Lp, bool* is_root_p, int* bid_p, int* nblocks_p) {
   const DevCtl* c = V.ctl;
-#ifdef LGBCU_STAGE_TIMERS
-  if (blockIdx.x == 0 && threadIdx.x == 0) g_hist_t0 = clock64();
-#endif
-  STAMP(V.ctl, 0);
-  // which leaf this block works for, and as which block of how many (one call site below: the body is large)
   DevLeaf L; bool is_root = false; int bid = blockIdx.x, nblocks = gridDim.x;
   if (leaf_arg >= 0) {
     L = V.leaves[leaf_arg]; is_root = leaf_arg == 0;
   } else {
-    if (c->done) return;
+    if (c->done) return false;
     if (c->round == 0) {
-      if (c->skip_find) return;
+      if (c->skip_find) return false;
       L = V.leaves[0]; is_root = true;
     } else {
       // The clusters of the grid are dealt to the round's leaves in proportion to their rows (at least one each), so
       // that the leaves are histogrammed side by side; a cluster works for exactly one leaf.
       const int ni = c->num_items;
-      const int nclusters = (int)gridDim.x / HIST_CLUSTER;
-      const int my_cluster = (int)blockIdx.x / HIST_CLUSTER, rank = (int)blockIdx.x % HIST_CLUSTER;
+      const int nclusters = (int)gridDim.x / unit;
+      const int my_cluster = (int)blockIdx.x / unit, rank = (int)blockIdx.x % unit;
       int rows[LGB_KMAX];
       long long total = 0;
       int live = 0;
@@ -315,7 +334,7 @@ __global__ void __cluster_dims__(HIST_CLUSTER, 1, 1) __launch_bounds__(HIST_THRE
         rows[e] = e < ni ? c->hist_rows[e] : 0;
         total += rows[e]; live += rows[e] != 0;
       }
-      if (live == 0) return;
+      if (live == 0) return false;
       const int spare = nclusters - live;
       // floor(rows * spare / total) without a 64-bit division: scaled down a hair so that float rounding can never
       // hand out more clusters than there are (every block computes the same numbers)
@@ -327,13 +346,40 @@ __global__ void __cluster_dims__(HIST_CLUSTER, 1, 1) __launch_bounds__(HIST_THRE
         const int nc = 1 + (int)((float)rows[e] * share);
         if (mine < 0 && my_cluster >= off && my_cluster < off + nc) {
           mine = e;
-          bid = (my_cluster - off) * HIST_CLUSTER + rank; nblocks = nc * HIST_CLUSTER;
+          bid = (my_cluster - off) * unit + rank; nblocks = nc * unit;
         }
         off += nc;
       }
-      if (mine < 0) return;
+      if (mine < 0) return false;
       L = c->hist_leaf[mine];
     }
   }
+  *Lp = L; *is_root_p = is_root; *bid_p = bid; *nblocks_p = nblocks;
+  return true;
+}
+
+__global__ void __cluster_dims__(HIST_CLUSTER, 1, 1) __launch_bounds__(HIST_THREADS, HIST_BLOCKS_PER_SM) k_hist(DevView V, int leaf_arg, int mode, int min_rows, int small_rows) {
+  extern __shared__ __align__(16) unsigned char hist_smem[];
+  const DevCtl* c = V.ctl;
+#ifdef LGBCU_STAGE_TIMERS
+  if (blockIdx.x == 0 && threadIdx.x == 0) g_hist_t0 = clock64();
+#endif
+  STAMP(V.ctl, 0);
+  DevLeaf L; bool is_root; int bid, nblocks;
+  if (!hist_pick_work(V, leaf_arg, HIST_CLUSTER, &L, &is_root, &bid, &nblocks)) return;
   hist_phase(V, L, is_root, mode, min_rows, small_rows, bid, nblocks, hist_smem);
+}
+
+
+// The same launch for data with a wide feature: no clusters, no sub-histograms (hist_global_wide_path).
+__global__ void __launch_bounds__(256) k_hist_wide(DevView V, int leaf_arg) {
+  STAMP(V.ctl, 0);
+  DevLeaf L; bool is_root; int bid, nblocks;
+  if (!hist_pick_work(V, leaf_arg, 1, &L, &is_root, &bid, &nblocks)) return;
+  const bool identity = V.ctl->root_identity && is_root && L.count == V.num_data;
+  hist_global_wide_path(V, L, identity, bid, nblocks);
+  if (bid == 0 && threadIdx.x == 0) {
+    atomicAdd(&V.ctl->prof_hist_calls, 1ull);
+    atomicAdd(identity ? &V.ctl->prof_hist_rows : &V.ctl->prof_hist_rows_indexed, (unsigned long long)L.count);
+  }
 }

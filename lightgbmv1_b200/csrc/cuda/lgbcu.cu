@@ -214,6 +214,7 @@ struct LgbCuContext {
   cudaStream_t stream = nullptr;
   // dataset
   int N = 0, F = 0, stride = 0, total_bin = 0, ntiles16 = 0;
+  int FS = 0; bool any_wide = false;   // byte columns of the matrices; some feature has more than 256 stored values
   uint8_t* d_bins = nullptr;
   DevFeat* d_feats = nullptr;
   std::vector<DevFeat> h_feats;
@@ -294,6 +295,7 @@ struct LgbCuContext {
   DevView view() const {
     DevView V;
     V.num_data = N; V.num_features = F; V.row_stride = stride; V.total_bin = total_bin; V.num_tiles16 = ntiles16;
+    V.num_storage = FS; V.any_wide = any_wide ? 1 : 0;
     V.bins = d_bins; V.feats = d_feats; V.feat_used = d_feat_used; V.splittable = d_splittable;
     V.parent_split = d_parent_split; V.mfb_fix = d_mfb_fix; V.spec = d_spec; V.expanded = d_expanded; V.pool_slots = pool_slots;
     V.bits_stride = bits_stride; V.part_sync_stride = part_sync_stride;
@@ -379,7 +381,8 @@ int ensure_tree_buffers(LgbCuContext* c) {
 
 int launch_hist(LgbCuContext* c, int leaf_arg) {
   const DevView V = c->view();
-  LAUNCH(k_hist, c->hist_grid, HIST_THREADS, HIST_SMEM_BYTES, c->stream, V, leaf_arg, c->hist_mode, c->hist_min_rows, c->hist_small_rows);
+  if (c->any_wide) LAUNCH(k_hist_wide, c->num_sms * 8, 256, 0, c->stream, V, leaf_arg);
+  else LAUNCH(k_hist, c->hist_grid, HIST_THREADS, HIST_SMEM_BYTES, c->stream, V, leaf_arg, c->hist_mode, c->hist_min_rows, c->hist_small_rows);
   CU(cudaGetLastError());
   return 0;
 }
@@ -404,7 +407,8 @@ int launch_partition(LgbCuContext* c, long long rows, int mode) {
   at[0].id = cudaLaunchAttributeCooperative;
   at[0].val.cooperative = 1;
   cfg.attrs = at; cfg.numAttrs = 1;
-  CU(cudaLaunchKernelEx(&cfg, k_partition, V, mode));
+  if (c->any_wide) CU(cudaLaunchKernelEx(&cfg, k_partition<true>, V, mode));
+  else CU(cudaLaunchKernelEx(&cfg, k_partition<false>, V, mode));
   g_launches.fetch_add(1, std::memory_order_relaxed);
   return 0;
 }
@@ -677,7 +681,8 @@ int lgbcu_create(int device_id, LgbCuContext** out) {
     CU(cudaDeviceGetAttribute(&coop, cudaDevAttrCooperativeLaunch, device_id));
     NEED(coop != 0, "lgbcu_create: device %d cannot do cooperative launches (needed by the fused partition)", device_id);
     int per_sm = 0;
-    CU(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, k_partition, PART_THREADS, 0));
+    CU(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, k_partition<false>, PART_THREADS, 0));
+    { int per_sm_w = 0; CU(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm_w, k_partition<true>, PART_THREADS, 0)); per_sm = std::min(per_sm, per_sm_w); }
     NEED(per_sm >= 2, "lgbcu_create: only %d k_partition block(s) fit on an SM", per_sm);
     // one slot per SM is left for the control block
     if (per_sm - 1 < c->part_blocks_per_sm) c->part_blocks_per_sm = per_sm - 1;
@@ -729,13 +734,11 @@ int lgbcu_synchronize(LgbCuContext* c) {
 static int setup_dataset_common(LgbCuContext* c, int32_t num_data, int32_t num_features, const LgbCuFeatureMeta* meta) {
   NEED(c, "lgbcu: NULL context");
   NEED(num_data > 0 && num_features > 0 && meta, "lgbcu_set_dataset: empty dataset");
-  NEED(num_features < (1 << KEY_FEAT_BITS), "lgbcu_set_dataset: %d features exceed the supported %d", num_features, (1 << KEY_FEAT_BITS) - 1);
   USE_DEVICE(c->device);
   c->N = num_data; c->F = num_features;
-  c->stride = (num_features + 15) & ~15;
-  c->ntiles16 = c->stride / 16;
   c->h_feats.resize(num_features);
-  int base = 0;
+  int base = 0, scol = 0;
+  c->any_wide = false;
   for (int f = 0; f < num_features; ++f) {
     DevFeat& d = c->h_feats[f];
     const LgbCuFeatureMeta& m = meta[f];
@@ -743,17 +746,26 @@ static int setup_dataset_common(LgbCuContext* c, int32_t num_data, int32_t num_f
     d.num_bin = m.num_bin; d.mfb = m.most_freq_bin; d.offset = m.most_freq_bin == 0 ? 1 : 0;
     d.default_bin = m.default_bin; d.missing_type = m.missing_type;
     d.hist_base = base; d.nslots = 1 + d.num_bin - d.offset;
-    NEED(d.nslots <= 256, "lgbcu_set_dataset: feature %d needs %d stored values; only 8-bit bins are supported "
-         "(max_bin <= 255)", f, d.nslots);
+    NEED(d.nslots <= 65536, "lgbcu_set_dataset: feature %d needs %d stored values; at most 16-bit bins are supported", f, d.nslots);
+    d.wide = d.nslots > 256 ? 1 : 0; d.col = scol; scol += d.wide ? 2 : 1;
+    c->any_wide = c->any_wide || d.wide;
     d.real_index = m.real_index; d.penalty = m.penalty;
     base += d.nslots;
   }
+  {
+    const int fb = c->any_wide ? KEY_FEAT_BITS_WIDE : KEY_FEAT_BITS;
+    NEED(num_features < (1 << fb), "lgbcu_set_dataset: %d features exceed the supported %d%s", num_features, (1 << fb) - 1,
+         c->any_wide ? " (for data with more than 256 bins in a feature)" : "");
+  }
   c->total_bin = base;
+  c->FS = scol;
+  c->stride = (c->FS + 15) & ~15;
+  c->ntiles16 = c->stride / 16;
   CU(dev_alloc(&c->d_feats, (size_t)num_features));
   CU(cudaMemcpyAsync(c->d_feats, c->h_feats.data(), sizeof(DevFeat) * num_features, cudaMemcpyHostToDevice, c->stream));
   CU(dev_alloc(&c->d_bins, (size_t)num_data * c->stride));
   c->col_stride = ((long long)num_data + 255) / 256 * 256;
-  CU(dev_alloc(&c->d_bins_col, (size_t)c->col_stride * num_features));
+  CU(dev_alloc(&c->d_bins_col, (size_t)c->col_stride * c->FS));
   CU(dev_alloc(&c->d_feat_used, (size_t)num_features));
   CU(cudaMemsetAsync(c->d_feat_used, 1, num_features, c->stream));
   CU(dev_alloc(&c->d_feat_best, (size_t)2 * LGB_KMAX * num_features));
@@ -791,14 +803,15 @@ int lgbcu_set_dataset(LgbCuContext* c, int32_t num_data, int32_t num_features, c
     // one contiguous H2D copy, then pad rows to the 16-byte stride on the device (a strided 2-D copy of 28-byte rows
     // crawls: one DMA descriptor per row)
     struct Tmp { uint8_t* p = nullptr; ~Tmp() { if (p) lgb_dev_free(p); } } packed;   // released on every way out
-    CU(dev_alloc(&packed.p, (size_t)num_data * num_features));
-    CU(cudaMemcpyAsync(packed.p, bins, (size_t)num_data * num_features, cudaMemcpyHostToDevice, c->stream));
+    // (the matrix has one byte column per feature, two -- low byte first -- per wide feature: c->FS in all)
+    CU(dev_alloc(&packed.p, (size_t)num_data * c->FS));
+    CU(cudaMemcpyAsync(packed.p, bins, (size_t)num_data * c->FS, cudaMemcpyHostToDevice, c->stream));
     LAUNCH(k_pad_rows, grid_for(c, (long long)num_data * (c->stride / 4), 256), 256, 0, c->stream, (long long)num_data,
-           num_features, c->stride, packed.p, c->d_bins);
+           c->FS, c->stride, packed.p, c->d_bins);
     CU(cudaGetLastError());
     CU(cudaStreamSynchronize(c->stream));
   }
-  LAUNCH(k_transpose_bins, grid_for(c, num_data, 256), 256, 0, c->stream, num_data, num_features, c->stride, c->d_bins,
+  LAUNCH(k_transpose_bins, grid_for(c, num_data, 256), 256, 0, c->stream, num_data, c->FS, c->stride, c->d_bins,
          c->d_bins_col, c->col_stride);
   CU(cudaGetLastError());
   CU(cudaStreamSynchronize(c->stream));
@@ -815,13 +828,14 @@ int lgbcu_set_dataset_columns(LgbCuContext* c, int32_t num_data, int32_t num_fea
   uint8_t** tmp = T.p;
   CU(dev_alloc(&tmp[0], (size_t)num_data));
   CU(dev_alloc(&tmp[1], (size_t)num_data));
+  NEED(!c->any_wide, "lgbcu_set_dataset_columns: a feature has more than 256 stored values; pass the byte matrix to lgbcu_set_dataset");
   for (int f = 0; f < num_features; ++f) {
     uint8_t* t = tmp[f & 1];
     if (f >= 2) CU(cudaStreamSynchronize(c->stream));  // the staging buffer two columns back is free again
     CU(cudaMemcpyAsync(t, columns[f], num_data, cudaMemcpyHostToDevice, c->stream));
     LAUNCH(k_scatter_column, grid_for(c, num_data, 256), 256, 0, c->stream, num_data, t, c->d_bins, c->stride, f);
   }
-  LAUNCH(k_transpose_bins, grid_for(c, num_data, 256), 256, 0, c->stream, num_data, num_features, c->stride, c->d_bins,
+  LAUNCH(k_transpose_bins, grid_for(c, num_data, 256), 256, 0, c->stream, num_data, c->FS, c->stride, c->d_bins,
          c->d_bins_col, c->col_stride);
   CU(cudaGetLastError());
   CU(cudaStreamSynchronize(c->stream));
@@ -1197,6 +1211,13 @@ int lgbcu_hist_build(LgbCuContext* c, int32_t leaf) {
   return 0;
 }
 
+// k_find_split comes in two instantiations so that data without wide features runs the kernel without the wide search
+// in it (the 8-bit kernel sits at its register cap: the extra code cost 0.1 ms per iteration when it was one kernel)
+static void launch_find_split(LgbCuContext* c, dim3 grid, const DevView& V, int mode, int leaf) {
+  if (c->any_wide) LAUNCH(k_find_split<true>, grid, FS_THREADS, 0, c->stream, V, mode, leaf);
+  else LAUNCH(k_find_split<false>, grid, FS_THREADS, 0, c->stream, V, mode, leaf);
+}
+
 int lgbcu_hist_read(LgbCuContext* c, int32_t leaf, double* out, int64_t out_len) {
   NEED(c && out && c->tree_begun, "lgbcu_hist_read: bad argument / no tree begun");
   NEED(out_len == 2LL * c->total_bin, "lgbcu_hist_read: out_len %lld != 2*total_bin %d", (long long)out_len, 2 * c->total_bin);
@@ -1221,7 +1242,7 @@ int lgbcu_find_best_split(LgbCuContext* c, int32_t leaf, LgbCuSplitInfo* out) {
   NEED(c && out && c->tree_begun, "lgbcu_find_best_split: bad argument / no tree begun");
   NEED(leaf >= 0 && leaf < c->params.num_leaves, "lgbcu_find_best_split: leaf %d out of range", leaf);
   USE_DEVICE(c->device);
-  LAUNCH(k_find_split, dim3(c->F, 1), FS_THREADS, 0, c->stream, c->view(), 1, leaf);
+  launch_find_split(c, dim3(c->F, 1), c->view(), 1, leaf);
   CU(cudaGetLastError());
   CU(cudaMemcpyAsync(c->h_split, c->d_best + leaf, sizeof(DevSplit), cudaMemcpyDeviceToHost, c->stream));
   CU(cudaStreamSynchronize(c->stream));
@@ -1317,11 +1338,12 @@ static int enqueue_round(LgbCuContext* c, int round, cudaEvent_t* ev) {
   if (ev) CU(cudaEventRecord(ev[1], c->stream));
   if (c->comm && c->dp_owner) {
     // owned scan -> all-gather of the winners -> control step
-    LAUNCH(k_find_split, dim3(V.f_end - V.f_begin, 2 * K), FS_THREADS, 0, c->stream, V, FS_MODE_OWNED, -1);
+    launch_find_split(c, dim3(V.f_end - V.f_begin, 2 * K), V, FS_MODE_OWNED, -1);
     if (comm_gather_winners(c)) return -1;
-    LAUNCH(k_find_split, dim3(1, 1), FS_THREADS, 0, c->stream, V, FS_MODE_CONTROL, -1);
-  } else
-  LAUNCH(k_find_split, dim3(c->F, 2 * K), FS_THREADS, 0, c->stream, V, 0, -1);
+    launch_find_split(c, dim3(1, 1), V, FS_MODE_CONTROL, -1);
+  } else {
+    launch_find_split(c, dim3(c->F, 2 * K), V, 0, -1);
+  }
   if (ev) CU(cudaEventRecord(ev[2], c->stream));
   if (launch_partition(c, c->root_count, 0)) return -1;
   if (ev) CU(cudaEventRecord(ev[3], c->stream));

@@ -386,7 +386,7 @@ __global__ void __launch_bounds__(256) k_add_score_tree(DevView V, TreeDev T, co
     while (node >= 0) {
       const int f = feat[node];
       const DevFeat F = V.feats[f];
-      const int stored = r[f];
+      const int stored = stored_bin_row(r, F);
       // DenseBinIterator::Get: stored value -> bin
       const int bin = stored == 0 ? F.mfb : stored - 1 + F.offset;
       const int missing_type = (dt[node] >> 2) & 3;

@@ -131,6 +131,9 @@ __device__ void part_expand(const DevView& V, int e, int leaf, const DevLeaf& L,
 #else
 #define PSTAGE(i) do {} while (0)
 #endif
+// WIDE: the data holds a feature with more than 256 stored values (two byte columns); a separate instantiation, so that
+// the 8-bit kernel keeps its registers
+template <bool WIDE>
 __global__ void __launch_bounds__(PART_THREADS, PART_BLOCKS_PER_SM + 1) k_partition(DevView V, int mode) {
   DevCtl* c = V.ctl;
 #ifdef LGBCU_STAGE_TIMERS
@@ -206,7 +209,8 @@ __global__ void __launch_bounds__(PART_THREADS, PART_BLOCKS_PER_SM + 1) k_partit
     // matrix one row's 32 features of which one byte is wanted.  (Round 1 used the row-major matrix below 1/16 of the
     // rows "to leave the row in L2 for the histogram pass": measured, the histogram pass does not notice and the
     // partition is 30 % faster without -- 1.15 vs 1.64 ms per iteration at 10.5M rows, 8.3 vs 12.0 ms at 100M.)
-    const uint8_t* col = V.bins_col + (size_t)feature * V.col_stride;
+    const uint8_t* col = V.bins_col + (size_t)F.col * V.col_stride;
+    const uint8_t* col_hi = col + V.col_stride;   // the high byte of a wide feature (max_bin > 255)
     int lefts = 0;
     // the row indices of tile k+1 are in flight while the bins of tile k are gathered
     int nrow[PART_REPS];
@@ -227,9 +231,13 @@ __global__ void __launch_bounds__(PART_THREADS, PART_BLOCKS_PER_SM + 1) k_partit
           nrow[r] = pos < L.count ? src[pos] : -1;
         }
       }
-      unsigned char bin[PART_REPS];
+      int bin[PART_REPS];
 #pragma unroll
       for (int r = 0; r < PART_REPS; ++r) bin[r] = row[r] >= 0 ? col[row[r]] : 0;
+      if (WIDE && F.wide) {
+#pragma unroll
+        for (int r = 0; r < PART_REPS; ++r) if (row[r] >= 0) bin[r] |= (int)col_hi[row[r]] << 8;
+      }
 #pragma unroll
       for (int r = 0; r < PART_REPS; ++r) {
         const bool left = row[r] >= 0 && goes_left(rule, bin[r]);

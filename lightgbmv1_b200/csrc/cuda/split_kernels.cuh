@@ -173,9 +173,21 @@ __device__ __forceinline__ void chain_lin(const double* __restrict__ in, double*
   *ah_io = ah;
 }
 // SplitKey::pad = inner feature | threshold << 20 | default_left << 29 (bins are 8-bit, so a threshold fits 9 bits)
-#define KEY_FEAT_BITS 20
+#define KEY_FEAT_BITS 20        /* 8-bit data: feature < 2^20, threshold in 10 bits */
+#define KEY_FEAT_BITS_WIDE 14   /* data with a wide feature: feature < 2^14, threshold in 16 bits */
+// pad = feature | threshold << fb | default_left << 30, fb by the data's kind (WIDE = the data has a wide feature;
+// a template argument so that the 8-bit kernel shifts by constants)
+template <bool WIDE>
 __device__ __forceinline__ int key_pack(int feature, int threshold, int default_left) {
-  return feature | (threshold << KEY_FEAT_BITS) | (default_left << (KEY_FEAT_BITS + 9));
+  constexpr int fb = WIDE ? KEY_FEAT_BITS_WIDE : KEY_FEAT_BITS;
+  return feature | (threshold << fb) | (default_left << 30);
+}
+template <bool WIDE>
+__device__ __forceinline__ void key_unpack(int pd, int* feature, int* threshold, int* default_left) {
+  constexpr int fb = WIDE ? KEY_FEAT_BITS_WIDE : KEY_FEAT_BITS;
+  *feature = pd & ((1 << fb) - 1);
+  *threshold = (pd >> fb) & ((1 << (30 - fb)) - 1);
+  *default_left = (pd >> 30) & 1;
 }
 
 #define FS_THREADS 256
@@ -578,6 +590,9 @@ __global__ void __launch_bounds__(XCHG_THREADS) k_xchg_pull(DevView V, XchgPeers
   xchg_finish(V, need);
 }
 
+#include "wide_split.cuh"
+
+template <bool WIDE>
 __device__ void find_item(const DevView& V, ScanSmem& S, int f, int sel, const FindTarget& T) {
   DevCtl* c = V.ctl;
   const int tid = threadIdx.x;
@@ -592,6 +607,7 @@ __device__ void find_item(const DevView& V, ScanSmem& S, int f, int sel, const F
     // them.  The data-parallel learner overrides FindBestSplits without that mask (data_parallel_tree_learner.cpp:
     // 155-173: every by-tree feature is histogrammed and scanned for every leaf), so there the flags are not applied.
     if (T.has_larger && T.parent_split && !V.data_parallel) used = used && T.parent_split[f] != 0;
+    if (WIDE && F.wide) { find_item_wide(V, S, f, sel, T, F, used != 0); return; }   // more than 256 stored values: the general search
     const int nt = F.num_bin - F.offset;
     const double inv_g = c->inv_g, inv_h = c->inv_h;
     HistEntry* hs = V.pool + (size_t)Ls.slot * V.total_bin + F.hist_base;  // smaller leaf, slot 0 of the group
@@ -627,7 +643,7 @@ __device__ void find_item(const DevView& V, ScanSmem& S, int f, int sel, const F
       }
       if (tid == 0) {
         V.feat_best[(size_t)T.slot * V.num_features + f] = o;
-        { SplitKey k; k.gain = o.gain; k.real_feature = o.real_feature; k.pad = o.feature >= 0 ? key_pack(o.feature, o.threshold, o.default_left) : 0; V.feat_key[(size_t)T.slot * V.num_features + f] = k; }
+        { SplitKey k; k.gain = o.gain; k.real_feature = o.real_feature; k.pad = o.feature >= 0 ? key_pack<WIDE>(o.feature, o.threshold, o.default_left) : 0; V.feat_key[(size_t)T.slot * V.num_features + f] = k; }
         V.splittable[(size_t)Ls.slot * V.num_features + f] = (int8_t)sp;
       }
     } else {
@@ -672,7 +688,7 @@ __device__ void find_item(const DevView& V, ScanSmem& S, int f, int sel, const F
       }
       if (tid == 0) {
         V.feat_best[(size_t)(T.slot + 1) * V.num_features + f] = o;
-        { SplitKey k; k.gain = o.gain; k.real_feature = o.real_feature; k.pad = o.feature >= 0 ? key_pack(o.feature, o.threshold, o.default_left) : 0; V.feat_key[(size_t)(T.slot + 1) * V.num_features + f] = k; }
+        { SplitKey k; k.gain = o.gain; k.real_feature = o.real_feature; k.pad = o.feature >= 0 ? key_pack<WIDE>(o.feature, o.threshold, o.default_left) : 0; V.feat_key[(size_t)(T.slot + 1) * V.num_features + f] = k; }
         if (used) V.splittable[(size_t)Ll.slot * V.num_features + f] = (int8_t)sp;
       }
     }
@@ -838,6 +854,7 @@ __device__ void commit_leaf(const DevView& V, int leaf, int lane) {
 }
 
 // warp 0, training: steps 2 and 3 of the control step -- general version, leaf keys re-read from memory every pass
+template <bool WIDE>
 __device__ void commit_and_select_global(const DevView& V, int lane) {
   DevCtl* c = V.ctl;
   int nl = c->num_leaves;
@@ -865,9 +882,7 @@ __device__ void commit_and_select_global(const DevView& V, int lane) {
       taken[ni] = bl;
       if (lane == 0) {
         c->item_leaf[ni] = bl;
-        c->item_feature[ni] = k.pad & ((1 << KEY_FEAT_BITS) - 1);
-        c->item_threshold[ni] = (k.pad >> KEY_FEAT_BITS) & 511;
-        c->item_default_left[ni] = (k.pad >> (KEY_FEAT_BITS + 9)) & 1;
+        key_unpack<WIDE>(k.pad, &c->item_feature[ni], &c->item_threshold[ni], &c->item_default_left[ni]);
       }
       ++ni;
     }
@@ -991,6 +1006,7 @@ __device__ void publish_items(const DevView& V) {
 //         the item's leaf, sel 1 forms larger = parent - smaller and scans it.  Round 0: only (item 0, sel 0) = root.
 // mode 1: one explicit leaf of the leaf table (step-wise API / tests), grid = (num_features, 1); result -> best[leaf].
 // The last block to finish runs the control step.
+template <bool WIDE>
 __global__ void __launch_bounds__(FS_THREADS, 4) k_find_split(DevView V, int mode, int leaf_arg) {
   __shared__ ScanSmem S;
   __shared__ int s_last;
@@ -1026,7 +1042,7 @@ __global__ void __launch_bounds__(FS_THREADS, 4) k_find_split(DevView V, int mod
   }
   STAGE(0);
   if (mode != FS_MODE_CONTROL) {
-    if (active && f < f_end) find_item(V, S, f, sel, T);
+    if (active && f < f_end) find_item<WIDE>(V, S, f, sel, T);
     STAGE(4);
     __threadfence();
     __syncthreads();
@@ -1154,7 +1170,7 @@ __global__ void __launch_bounds__(FS_THREADS, 4) k_find_split(DevView V, int mod
   __syncthreads();
   const int nl0 = c->num_leaves, ns0 = c->num_splits;
   if (V.p.num_leaves > CTRL_MAX_LEAVES) {  // big trees: the general, sequential version
-    if (warp == 0) commit_and_select_global(V, lane);
+    if (warp == 0) commit_and_select_global<WIDE>(V, lane);
     publish_items(V);
     return;
   }
@@ -1202,9 +1218,7 @@ __global__ void __launch_bounds__(FS_THREADS, 4) k_find_split(DevView V, int mod
       if (rank < K) {
         const int pd = C.pad[l];
         c->item_leaf[rank] = l;
-        c->item_feature[rank] = pd & ((1 << KEY_FEAT_BITS) - 1);
-        c->item_threshold[rank] = (pd >> KEY_FEAT_BITS) & 511;
-        c->item_default_left[rank] = (pd >> (KEY_FEAT_BITS + 9)) & 1;
+        key_unpack<WIDE>(pd, &c->item_feature[rank], &c->item_threshold[rank], &c->item_default_left[rank]);
       }
     }
     const int n_elig = n_el;

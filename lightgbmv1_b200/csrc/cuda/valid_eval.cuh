@@ -53,10 +53,10 @@ int lgbcu_valid_create(LgbCuContext* c, int32_t num_data, const uint8_t* bins, i
   CU(dev_alloc(&v.d_bins, (size_t)num_data * c->stride));
   {
     struct Tmp { uint8_t* p = nullptr; ~Tmp() { if (p) lgb_dev_free(p); } } packed;   // released on every way out
-    CU(dev_alloc(&packed.p, (size_t)num_data * c->F));
-    CU(cudaMemcpyAsync(packed.p, bins, (size_t)num_data * c->F, cudaMemcpyHostToDevice, c->stream));
+    CU(dev_alloc(&packed.p, (size_t)num_data * c->FS));
+    CU(cudaMemcpyAsync(packed.p, bins, (size_t)num_data * c->FS, cudaMemcpyHostToDevice, c->stream));
     LAUNCH(k_pad_rows, grid_for(c, (long long)num_data * (c->stride / 4), 256), 256, 0, c->stream, (long long)num_data,
-           c->F, c->stride, packed.p, v.d_bins);
+           c->FS, c->stride, packed.p, v.d_bins);
     CU(cudaGetLastError());
     CU(cudaStreamSynchronize(c->stream));
   }

@@ -607,11 +607,16 @@ int LGBM_B200_DatasetDumpBins(DatasetHandle handle, int32_t* out_bins, int32_t* 
   API_BEGIN();
   const Dataset* ds = reinterpret_cast<Dataset*>(handle);
   const int F = ds->num_features(), N = ds->num_data();
+  const int FS = ds->num_storage_columns();
+  std::vector<int> scol(F), wide(F);
+  for (int f = 0, s = 0; f < F; ++f) { wide[f] = ds->stored_values(f) > 256; scol[f] = s; s += wide[f] ? 2 : 1; }
+  const std::vector<uint8_t>& bytes = ds->bins();
   for (int f = 0; f < F; ++f) real_index[f] = ds->real_feature_index(f);
   for (int r = 0; r < N; ++r) {
     for (int f = 0; f < F; ++f) {
       const BinMapper& m = ds->mapper(f);
-      const int stored = ds->bins()[static_cast<size_t>(r) * F + f];
+      const uint8_t* p = bytes.data() + static_cast<size_t>(r) * FS + scol[f];
+      const int stored = wide[f] ? (p[0] | (p[1] << 8)) : p[0];
       const int offset = m.most_freq_bin() == 0 ? 1 : 0;
       out_bins[static_cast<size_t>(r) * F + f] = stored == 0 ? static_cast<int>(m.most_freq_bin()) : stored - 1 + offset;
     }

@@ -265,6 +265,7 @@ void Config::Set(const std::unordered_map<std::string, std::string>& p) {
   if (num_leaves <= 1 || num_leaves > 131072) Log::Fatal("num_leaves should be in (1, 131072], got %d", num_leaves);
   if (learning_rate <= 0.0) Log::Fatal("learning_rate should be > 0");
   if (max_bin <= 1) Log::Fatal("max_bin should be > 1");
+  if (max_bin > 65535) Log::Fatal("max_bin should be <= 65535 (8- and 16-bit bins are built), got %d", max_bin);
   if (min_data_in_leaf < 0) Log::Fatal("min_data_in_leaf should be >= 0");
   if (min_sum_hessian_in_leaf < 0) Log::Fatal("min_sum_hessian_in_leaf should be >= 0");
   if (bagging_fraction <= 0.0 || bagging_fraction > 1.0) Log::Fatal("bagging_fraction should be in (0, 1]");

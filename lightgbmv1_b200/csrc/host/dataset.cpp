@@ -237,8 +237,8 @@ Dataset* Dataset::FromDenseMatrix(const void* data, int data_type, int32_t nrow,
   }
   ds->real_to_inner_.assign(ncol, -1);
   for (int f : order) {
-    if (all[f]->num_bin() + (all[f]->most_freq_bin() == 0 ? 0 : 1) > 256) {
-      Log::Fatal("feature %d needs more than 256 stored values; only 8-bit bins (max_bin <= 255) are built", f);
+    if (all[f]->num_bin() + (all[f]->most_freq_bin() == 0 ? 0 : 1) > 65536) {
+      Log::Fatal("feature %d needs more than 65536 stored values; at most 16-bit bins are built", f);
     }
     ds->real_to_inner_[f] = static_cast<int>(ds->inner_to_real_.size());
     ds->inner_to_real_.push_back(f);
@@ -302,11 +302,20 @@ void Dataset::BinAllRows(const void* data, int data_type, int32_t nrow, int32_t 
     return;
   }
   const MatView M{data, data_type, nrow, ncol, row_major};
-  bins_.assign(static_cast<size_t>(nrow) * std::max(F, 1), 0);
+  // byte matrix: one column per feature, two (low byte first) per feature with more than 256 stored values -- the
+  // layout lgbcu_set_dataset / lgbcu_bin_matrix use
+  std::vector<int> scol(F), wide(F);
+  int FS = 0;
+  for (int f = 0; f < F; ++f) { wide[f] = stored_values(f) > 256; scol[f] = FS; FS += wide[f] ? 2 : 1; }
+  bins_.assign(static_cast<size_t>(nrow) * std::max(FS, 1), 0);
 #pragma omp parallel for schedule(static)
   for (int32_t r = 0; r < nrow; ++r) {
-    uint8_t* out = bins_.data() + static_cast<size_t>(r) * F;
-    for (int f = 0; f < F; ++f) out[f] = static_cast<uint8_t>(stored_value(f, M.at(r, inner_to_real_[f])));
+    uint8_t* out = bins_.data() + static_cast<size_t>(r) * FS;
+    for (int f = 0; f < F; ++f) {
+      const uint32_t v = stored_value(f, M.at(r, inner_to_real_[f]));
+      out[scol[f]] = static_cast<uint8_t>(v & 255u);
+      if (wide[f]) out[scol[f] + 1] = static_cast<uint8_t>(v >> 8);
+    }
   }
   // the matrix only exists to be uploaded: page-lock it (a no-op without a device)
   bins_pinned_ = lgbcu_pin_host_buffer(bins_.data(), bins_.size()) == 0;
@@ -314,7 +323,7 @@ void Dataset::BinAllRows(const void* data, int data_type, int32_t nrow, int32_t 
 
 const std::vector<uint8_t>& Dataset::bins() const {
   if (bins_.empty() && dev_bins_ != nullptr) {
-    bins_.assign(static_cast<size_t>(num_data_) * std::max(num_features(), 1), 0);
+    bins_.assign(static_cast<size_t>(num_data_) * std::max(num_storage_columns(), 1), 0);
     if (lgbcu_binned_copy_to_host(dev_bins_, bins_.data()) != 0) Log::Fatal("%s", lgbcu_last_error());
   }
   return bins_;

@@ -36,6 +36,10 @@ class Dataset {
 
   data_size_t num_data() const { return num_data_; }
   int num_features() const { return static_cast<int>(inner_to_real_.size()); }
+  // stored values of an inner feature (FeatureGroup::num_total_bin_ of its single-feature group) and the byte columns of
+  // the binned matrix: one per feature, two for a feature with more than 256 stored values (max_bin > 255)
+  int stored_values(int inner) const { return mappers_[inner]->num_bin() + (mappers_[inner]->most_freq_bin() == 0 ? 0 : 1); }
+  int num_storage_columns() const { int n = 0; for (int f = 0; f < num_features(); ++f) n += stored_values(f) > 256 ? 2 : 1; return n; }
   int num_total_features() const { return num_total_features_; }
   int real_feature_index(int inner) const { return inner_to_real_[inner]; }
   int inner_feature_index(int real) const { return real_to_inner_[real]; }
