@@ -124,8 +124,11 @@ LGBCU_API int lgbcu_create(int device_id, LgbCuContext** out);
 LGBCU_API int lgbcu_destroy(LgbCuContext* ctx);
 LGBCU_API int lgbcu_synchronize(LgbCuContext* ctx);
 
-/* A2: make the binned matrix resident.  `bins` is row-major [num_data][num_features] (host); it is copied
- * into a row-major device matrix whose row stride is num_features rounded up to a multiple of 16 bytes.
+/* A2: make the binned matrix resident.  `bins` is a row-major byte matrix [num_data][FS] (host), FS = one byte column
+ * per feature, and two -- low byte, then high byte -- for a feature with more than 256 stored values
+ * (1 + num_bin - [most_freq_bin == 0] > 256, i.e. max_bin > 255: the reference's 16-bit DenseBin, src/io/bin.cpp:
+ * 635-645); FS = num_features when every feature fits a byte.  It is copied into a row-major device matrix whose row
+ * stride is FS rounded up to a multiple of 16 bytes.
  * Replaces FeatureGroup/DenseBin storage (src/io/dense_bin.hpp:55-81) + TreeLearner::Init's view of it
  * (src/treelearner/serial_tree_learner.cpp:28-69). */
 LGBCU_API int lgbcu_set_dataset(LgbCuContext* ctx, int32_t num_data, int32_t num_features,
