@@ -46,7 +46,9 @@ enum { LGBCU_MISSING_NONE = 0, LGBCU_MISSING_ZERO = 1, LGBCU_MISSING_NAN = 2 };
 enum { LGBCU_OBJ_NONE = 0, LGBCU_OBJ_BINARY = 1, LGBCU_OBJ_L2 = 2, LGBCU_OBJ_LAMBDARANK = 3, LGBCU_OBJ_MULTICLASS = 4,
        LGBCU_OBJ_L1 = 5, LGBCU_OBJ_QUANTILE = 6, LGBCU_OBJ_MULTICLASSOVA = 7,
        LGBCU_OBJ_HUBER = 8 /* p0 = alpha */, LGBCU_OBJ_FAIR = 9 /* p0 = fair_c */, LGBCU_OBJ_POISSON = 10 /* p0 = poisson_max_delta_step */,
-       LGBCU_OBJ_GAMMA = 11, LGBCU_OBJ_TWEEDIE = 12 /* p0 = tweedie_variance_power */ };
+       LGBCU_OBJ_GAMMA = 11, LGBCU_OBJ_TWEEDIE = 12 /* p0 = tweedie_variance_power */,
+       LGBCU_OBJ_XENTROPY = 13 /* cross_entropy: labels in [0, 1] */,
+       LGBCU_OBJ_MAPE = 14 /* L1 with the per-row weight 1 / max(1, |label|); no user weights */ };
 /* histogram kernel selection (LGBCU_HIST_AUTO picks by leaf size) */
 enum { LGBCU_HIST_AUTO = 0, LGBCU_HIST_GLOBAL_ATOMIC = 1, LGBCU_HIST_WARP_PRIVATE = 2 };
 
@@ -142,7 +144,7 @@ LGBCU_API int lgbcu_set_dataset_columns(LgbCuContext* ctx, int32_t num_data, int
  * (BinMapper::FindBin); this call uploads the raw matrix once (float32 data_type 0 / float64 data_type 1, row- or
  * column-major) and bins every (row, inner feature) with the reference's binary search over the feature's upper
  * bounds (upper_bounds[bound_offset .. bound_offset + num_bin)) -- bit-identical to the host map.  The result, a
- * row-major [nrow][num_features] matrix of stored values, stays on the device: lgbcu_set_dataset_binned makes it a
+ * row-major [nrow][FS] byte matrix of stored values (FS as for lgbcu_set_dataset), stays on the device: lgbcu_set_dataset_binned makes it a
  * learner's resident matrix without a host round trip, lgbcu_binned_copy_to_host reads it back. */
 typedef struct LgbCuBinnedMatrix LgbCuBinnedMatrix;
 typedef struct LgbCuBinFeature {
@@ -151,7 +153,11 @@ typedef struct LgbCuBinFeature {
   int32_t most_freq_bin;
   int32_t missing_type;   /* LGBCU_MISSING_* */
   int32_t bound_offset;   /* first upper bound of this feature in upper_bounds */
-  int32_t reserved;
+  int32_t bundle;         /* 0: a feature of its own.  b > 0: member of exclusive-feature bundle b (the reference's
+                           * multi-feature FeatureGroup over ONE DenseBin, include/LightGBM/feature_group.h:32-50): in a
+                           * row where several members are off their most-frequent bin, only the member with the
+                           * highest `column` keeps its value (the reference's pushes overwrite one another in column
+                           * order, dataset.h:382-392 -> dense_bin.hpp:68-80); the others read as most-frequent */
 } LgbCuBinFeature;
 LGBCU_API int lgbcu_bin_matrix(int device, const void* data, int data_type, int32_t nrow, int32_t ncol, int is_row_major,
                                int32_t num_features, const LgbCuBinFeature* feats, const double* upper_bounds,
@@ -348,6 +354,9 @@ LGBCU_API int lgbcu_valid_copy_score(LgbCuContext* ctx, int32_t set, double* out
 #define LGBCU_METRIC_GAMMA 12
 #define LGBCU_METRIC_TWEEDIE 13        /* `sigmoid` = tweedie_variance_power */
 #define LGBCU_METRIC_BINARY_ERROR 14   /* `sigmoid` as for binary_logloss */
+#define LGBCU_METRIC_MAPE 16
+#define LGBCU_METRIC_XENTROPY 15       /* cross_entropy (labels in [0, 1]); `sigmoid` as for binary_logloss.  kullback_leibler is
+                                        * this plus a constant of the labels, which the host adds */
 LGBCU_API int lgbcu_eval_set_ndcg(LgbCuContext* ctx, int32_t set, const int32_t* eval_at, int32_t num_eval,
                                   const double* inv_max_dcg, const float* query_weight, const double* label_gain,
                                   int32_t num_label_gain, const double* discount, int32_t num_discount);

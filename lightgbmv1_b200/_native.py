@@ -152,8 +152,12 @@ class CudaLearner:
         bins = np.ascontiguousarray(bins, dtype=np.uint8)
         assert bins.ndim == 2
         self._metas = metas if isinstance(metas, C.Array) else make_feature_meta(metas)
-        self.num_data, self.num_features = bins.shape
-        check(lib.lgbcu_set_dataset(self._h, C.c_int32(bins.shape[0]), C.c_int32(bins.shape[1]),
+        # byte columns: one per feature, two (low byte first) for a feature with more than 256 stored values
+        self.num_data, self.num_features = bins.shape[0], len(self._metas)
+        fs = sum(2 if 1 + m.num_bin - (1 if m.most_freq_bin == 0 else 0) > 256 else 1 for m in self._metas)
+        if fs != bins.shape[1]:
+            raise LgbCuError(f"set_dataset: {len(self._metas)} feature descriptors need {fs} byte columns, the matrix has {bins.shape[1]}")
+        check(lib.lgbcu_set_dataset(self._h, C.c_int32(bins.shape[0]), C.c_int32(self.num_features),
                                     _ptr(bins, C.c_uint8), self._metas))
 
     def set_dataset_columns(self, columns, metas) -> None:

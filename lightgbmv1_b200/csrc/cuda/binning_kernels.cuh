@@ -47,6 +47,31 @@ __global__ void __launch_bounds__(256) k_bin_rows(const T* __restrict__ x, long 
   }
 }
 
+// Exclusive-feature bundles (LgbCuBinFeature::bundle): the reference keeps the members of a bundle in ONE column, so in
+// a row where several members are off their most-frequent bin the pushes overwrite one another and the member pushed
+// last -- the highest raw column -- survives; to every other member the row reads as most-frequent (its value lies
+// outside their ranges: DenseBin::SplitInner / DenseBinIterator::Get with min_bin / max_bin, dense_bin.hpp:173-307,
+// 446-460; the histogram leaves it to FixHistogram).  Here every feature has its own column(s), so the same rows are
+// set to 0 after the map.  One thread per (row, bundle); `mem` lists a bundle's members by DESCENDING raw column.
+struct BundleMember { int scol, wide; };
+__global__ void __launch_bounds__(256) k_bundle_override(uint8_t* __restrict__ out, long long rows, int FS, int nb,
+                                                         const int* __restrict__ start, const BundleMember* __restrict__ mem) {
+  const long long total = rows * nb;
+  for (long long i = blockIdx.x * (long long)blockDim.x + threadIdx.x; i < total; i += (long long)gridDim.x * blockDim.x) {
+    const long long r = i / nb;
+    const int b = (int)(i - r * nb);
+    uint8_t* o = out + r * FS;
+    bool seen = false;
+    for (int m = start[b]; m < start[b + 1]; ++m) {
+      const BundleMember M = mem[m];
+      const int v = o[M.scol] | (M.wide ? o[M.scol + 1] << 8 : 0);
+      if (v == 0) continue;
+      if (seen) { o[M.scol] = 0; if (M.wide) o[M.scol + 1] = 0; }
+      seen = true;
+    }
+  }
+}
+
 // Page-locked staging for lgbcu_bin_matrix, kept between calls: allocating 2 x 64 MB of pinned memory costs ~35 ms, a
 // third of binning 10.5M x 28 -- and datasets are created more than once per process (validation sets, shards,
 // repeated training).  One pair per process, handed to one caller at a time; a concurrent caller allocates its own.
@@ -91,7 +116,7 @@ int lgbcu_bin_matrix(int device, const void* data, int data_type, int32_t nrow, 
   NEED(device >= 0 && device < ndev, "lgbcu_bin_matrix: device %d out of range (have %d)", device, ndev);
   USE_DEVICE(device);
   struct Guard {   // everything but the result is released on every way out
-    void* dev[4] = {nullptr, nullptr, nullptr, nullptr}; void* pin[2] = {nullptr, nullptr}; bool pin_cached = false;
+    void* dev[6] = {nullptr, nullptr, nullptr, nullptr, nullptr, nullptr}; void* pin[2] = {nullptr, nullptr}; bool pin_cached = false;
     cudaStream_t s[2] = {nullptr, nullptr}; cudaEvent_t ev[2] = {nullptr, nullptr}; LgbCuBinnedMatrix* m = nullptr;
     ~Guard() {
       for (void* p : dev) if (p) lgb_dev_free(p);
@@ -118,6 +143,24 @@ int lgbcu_bin_matrix(int device, const void* data, int data_type, int32_t nrow, 
   }
   int FS = 0;   // byte columns of the result
   for (int f = 0; f < num_features; ++f) { hf[f].scol = FS; FS += (hf[f].num_bin + (hf[f].mfb == 0 ? 0 : 1) > 256) ? 2 : 1; }
+  // exclusive-feature bundles: members by descending raw column
+  int nb = 0;
+  for (int f = 0; f < num_features; ++f) { NEED(feats[f].bundle >= 0, "lgbcu_bin_matrix: bad bundle of feature %d", f); nb = std::max(nb, (int)feats[f].bundle); }
+  int* d_bstart = nullptr; BundleMember* d_bmem = nullptr;
+  if (nb > 0) {
+    std::vector<std::vector<int>> members(nb);
+    for (int f = 0; f < num_features; ++f) if (feats[f].bundle > 0) members[feats[f].bundle - 1].push_back(f);
+    std::vector<int> bstart(1, 0); std::vector<BundleMember> bmem;
+    for (auto& g : members) {
+      std::sort(g.begin(), g.end(), [&](int a, int b) { return feats[a].column > feats[b].column; });
+      for (int f : g) bmem.push_back(BundleMember{hf[f].scol, (hf[f].num_bin + (hf[f].mfb == 0 ? 0 : 1) > 256) ? 1 : 0});
+      bstart.push_back((int)bmem.size());
+    }
+    CU(lgb_dev_malloc(&G.dev[4], sizeof(int) * bstart.size())); d_bstart = static_cast<int*>(G.dev[4]);
+    CU(lgb_dev_malloc(&G.dev[5], sizeof(BundleMember) * std::max<size_t>(1, bmem.size()))); d_bmem = static_cast<BundleMember*>(G.dev[5]);
+    CU(cudaMemcpy(d_bstart, bstart.data(), sizeof(int) * bstart.size(), cudaMemcpyHostToDevice));
+    CU(cudaMemcpy(d_bmem, bmem.data(), sizeof(BundleMember) * bmem.size(), cudaMemcpyHostToDevice));
+  }
   BinFeatDev* d_feats = nullptr; double* d_bounds = nullptr;
   CU(lgb_dev_malloc(&G.dev[0], sizeof(BinFeatDev) * num_features)); d_feats = static_cast<BinFeatDev*>(G.dev[0]);
   CU(lgb_dev_malloc(&G.dev[1], sizeof(double) * num_bounds)); d_bounds = static_cast<double*>(G.dev[1]);
@@ -162,6 +205,11 @@ int lgbcu_bin_matrix(int device, const void* data, int data_type, int32_t nrow, 
       if (data_type == 0) k_bin_rows<float><<<grid, 256, 0, G.s[b]>>>(static_cast<const float*>(G.dev[2 + b]), (long long)rows, ncol, 1, 0, num_features, FS, d_feats, d_bounds, dst);
       else k_bin_rows<double><<<grid, 256, 0, G.s[b]>>>(static_cast<const double*>(G.dev[2 + b]), (long long)rows, ncol, 1, 0, num_features, FS, d_feats, d_bounds, dst);
       g_launches.fetch_add(1, std::memory_order_relaxed);
+      if (nb > 0) {
+        const int bgrid = (int)std::min<long long>(max_grid, ((long long)rows * nb + 255) / 256);
+        k_bundle_override<<<bgrid, 256, 0, G.s[b]>>>(dst, (long long)rows, FS, nb, d_bstart, d_bmem);
+        g_launches.fetch_add(1, std::memory_order_relaxed);
+      }
       CU(cudaGetLastError());
     }
   } else {
@@ -180,6 +228,11 @@ int lgbcu_bin_matrix(int device, const void* data, int data_type, int32_t nrow, 
     if (data_type == 0) k_bin_rows<float><<<grid, 256, 0, G.s[0]>>>(static_cast<const float*>(G.dev[2]), (long long)nrow, num_features, 0, (long long)nrow, num_features, FS, d_feats, d_bounds, G.m->d_bins);
     else k_bin_rows<double><<<grid, 256, 0, G.s[0]>>>(static_cast<const double*>(G.dev[2]), (long long)nrow, num_features, 0, (long long)nrow, num_features, FS, d_feats, d_bounds, G.m->d_bins);
     g_launches.fetch_add(1, std::memory_order_relaxed);
+    if (nb > 0) {
+      const int bgrid = (int)std::min<long long>(max_grid, ((long long)nrow * nb + 255) / 256);
+      k_bundle_override<<<bgrid, 256, 0, G.s[0]>>>(G.m->d_bins, (long long)nrow, FS, nb, d_bstart, d_bmem);
+      g_launches.fetch_add(1, std::memory_order_relaxed);
+    }
     CU(cudaGetLastError());
   }
   tick("chunks enqueued");

@@ -70,6 +70,10 @@ __global__ void k_grad_regression(int n, int kind, double p0, const double* __re
     } else if (kind == LGBCU_OBJ_TWEEDIE) { // RegressionTweedieLoss (:720-738); p0 = tweedie_variance_power
       g = -label[i] * exp((1 - p0) * score[i]) + exp((2 - p0) * score[i]);
       h = -label[i] * (1 - p0) * exp((1 - p0) * score[i]) + (2 - p0) * exp((2 - p0) * score[i]);
+    } else if (kind == LGBCU_OBJ_XENTROPY) { // CrossEntropy::GetGradients (xentropy_objective.hpp:77-96)
+      const double z = 1.0f / (1.0f + exp(-score[i]));
+      g = z - label[i];
+      h = z * (1.0f - z);
     } else {  // poisson
       g = exp(score[i]) - label[i];
       h = exp(score[i] + p0);
@@ -79,13 +83,17 @@ __global__ void k_grad_regression(int n, int kind, double p0, const double* __re
   }
 }
 
+__device__ __forceinline__ float mape_label_weight(float label) { return 1.0f / fmaxf(1.0f, fabsf(label)); }
+
 // RegressionL1loss::GetGradients (src/objective/regression_objective.hpp:214-231): sign(score - label) [* w], hessian 1 [w]
 __global__ void k_grad_l1(int n, const double* __restrict__ score, const float* __restrict__ label,
-                          const float* __restrict__ weight, float* __restrict__ grad, float* __restrict__ hess) {
+                          const float* __restrict__ weight, float* __restrict__ grad, float* __restrict__ hess, int mape) {
   for (int i = blockIdx.x * blockDim.x + threadIdx.x; i < n; i += gridDim.x * blockDim.x) {
     const double diff = score[i] - label[i];
     const int sg = (diff > 0.0) - (diff < 0.0);   // Common::Sign
-    if (weight == nullptr) { grad[i] = (float)sg; hess[i] = 1.0f; }
+    // RegressionMAPELOSS (:587-626, unweighted): label_weight_ = 1 / max(1, |label|) scales the gradient only
+    if (mape) { grad[i] = (float)(sg * mape_label_weight(label[i])); hess[i] = 1.0f; }
+    else if (weight == nullptr) { grad[i] = (float)sg; hess[i] = 1.0f; }
     else { grad[i] = (float)(sg * weight[i]); hess[i] = weight[i]; }
   }
 }

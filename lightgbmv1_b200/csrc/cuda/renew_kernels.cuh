@@ -15,7 +15,7 @@
 #pragma once
 
 __global__ void k_renew_gather(DevView V, int num_leaves, const double* __restrict__ score, const float* __restrict__ label,
-                               const float* __restrict__ weight, double* __restrict__ keys, float* __restrict__ wout,
+                               const float* __restrict__ weight, int mape, double* __restrict__ keys, float* __restrict__ wout,
                                int* __restrict__ seg, int* __restrict__ seg_begin, int* __restrict__ seg_end) {
   const int l = blockIdx.x;
   if (l >= num_leaves) return;
@@ -25,7 +25,7 @@ __global__ void k_renew_gather(DevView V, int num_leaves, const double* __restri
   for (int p = blockIdx.y * blockDim.x + threadIdx.x; p < L.count; p += gridDim.y * blockDim.x) {
     const int row = idx[p];
     keys[L.begin + p] = (double)label[row] - score[row];   // residual_getter (gbdt.cpp:372)
-    if (wout) wout[L.begin + p] = weight[row];
+    if (wout) wout[L.begin + p] = mape ? mape_label_weight(label[row]) : weight[row];   // mape: RegressionMAPELOSS::label_weight_
     if (seg) seg[L.begin + p] = l;
   }
 }
@@ -88,7 +88,8 @@ extern "C" int lgbcu_renew_leaf_outputs(LgbCuContext* c, int32_t num_leaves, dou
   NEED(c->has_label, "lgbcu_renew_leaf_outputs: label not set");
   USE_DEVICE(c->device);
   const int n = c->root_count;          // rows the tree grew on (the bag)
-  const bool weighted = c->has_weight;
+  const bool mape = c->objective == LGBCU_OBJ_MAPE;
+  const bool weighted = c->has_weight || mape;
   if (c->renew_cap < n) {
     CU(dev_alloc(&c->d_renew_key[0], (size_t)n)); CU(dev_alloc(&c->d_renew_key[1], (size_t)n));
     CU(dev_alloc(&c->d_renew_w[0], (size_t)n)); CU(dev_alloc(&c->d_renew_w[1], (size_t)n));
@@ -102,7 +103,7 @@ extern "C" int lgbcu_renew_leaf_outputs(LgbCuContext* c, int32_t num_leaves, dou
   }
   const DevView V = c->view();
   LAUNCH(k_renew_gather, dim3(num_leaves, 64), 256, 0, c->stream, V, (int)num_leaves, c->d_score, c->d_label,
-         weighted ? c->d_weight : nullptr, c->d_renew_key[0], weighted ? c->d_renew_w[0] : nullptr,
+         c->has_weight ? c->d_weight : nullptr, mape ? 1 : 0, c->d_renew_key[0], weighted ? c->d_renew_w[0] : nullptr,
          weighted ? c->d_renew_seg : nullptr, c->d_renew_begin, c->d_renew_end);
   size_t need = 0;
   if (weighted) {

@@ -112,6 +112,9 @@ std::string ObjectiveAlias(std::string t) {
   if (t == "multiclass" || t == "softmax") return "multiclass";
   if (t == "multiclassova" || t == "multiclass_ova" || t == "ova" || t == "ovr") return "multiclassova";
   if (t == "regression_l1" || t == "mean_absolute_error" || t == "l1" || t == "mae") return "regression_l1";
+  if (t == "xentropy" || t == "cross_entropy") return "cross_entropy";
+  if (t == "xentlambda" || t == "cross_entropy_lambda") return "cross_entropy_lambda";
+  if (t == "mean_absolute_percentage_error" || t == "mape") return "mape";
   return t;
 }
 

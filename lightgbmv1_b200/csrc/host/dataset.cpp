@@ -35,9 +35,11 @@ struct MatView {
   }
 };
 
-// ---- Exclusive-feature-bundling decision (src/io/dataset.cpp:50-313).  Only the grouping DECISION and the
-// resulting feature order are reproduced: this library stores every feature as its own group.  A bundle that
-// would share one column between several features (which may drop conflicting rows) is refused.
+// ---- Exclusive-feature-bundling decision (src/io/dataset.cpp:50-313).  The grouping DECISION and the resulting
+// feature order are reproduced; the storage is not: this library keeps every feature in its own column(s).  What a
+// shared column changes in the reference's results -- in a row where two features of a bundle are both off their
+// most-frequent bin, the later push overwrites the earlier one -- is applied to the binned matrix instead
+// (BinAllRows / lgbcu_bin_matrix: LgbCuBinFeature::bundle), so bundled data trains to the same trees.
 int ConflictCount(const std::vector<bool>& mark, const std::vector<int>& idx, int max_cnt) {
   int ret = 0;
   for (int i : idx) {
@@ -124,9 +126,11 @@ std::vector<std::vector<int>> FindGroups(const std::vector<std::shared_ptr<BinMa
 }
 
 // FastFeatureBundling (src/io/dataset.cpp:236-313) -> inner feature order
+// `bundle_of_real`: per raw column, 0 or the 1-based id of the single-column bundle it belongs to
 std::vector<int> BundledFeatureOrder(const std::vector<std::shared_ptr<BinMapper>>& mappers,
                                      const std::vector<int>& used, const std::vector<std::vector<double>>& sample_vals,
-                                     std::vector<std::vector<int>> sample_idx, int total_sample_cnt, data_size_t num_data) {
+                                     std::vector<std::vector<int>> sample_idx, int total_sample_cnt, data_size_t num_data,
+                                     std::vector<int>* bundle_of_real) {
   // FixSampleIndices: when the most frequent bin is not the zero bin, "non-zero" means "not in the most frequent bin"
   for (int f : used) {
     const BinMapper& m = *mappers[f];
@@ -163,12 +167,11 @@ std::vector<int> BundledFeatureOrder(const std::vector<std::shared_ptr<BinMapper
     std::swap(mv1[i], mv1[j]);
   }
   std::vector<int> order;
+  int next_bundle = 0;
   for (int g = 0; g < ng; ++g) {
-    if (g1[g].size() > 1 && !mv1[g]) {
-      Log::Fatal("exclusive feature bundling would merge %d sparse features into one column; bundled groups are "
-                 "outside this library's path -- pass enable_bundle=false", static_cast<int>(g1[g].size()));
-    }
-    for (int f : g1[g]) order.push_back(f);
+    // a multi-value group keeps one bin per feature (FeatureGroup::multi_bin_data_): nothing is overwritten there
+    const int id = (g1[g].size() > 1 && !mv1[g]) ? ++next_bundle : 0;
+    for (int f : g1[g]) { order.push_back(f); (*bundle_of_real)[f] = id; }
   }
   return order;
 }
@@ -232,8 +235,9 @@ Dataset* Dataset::FromDenseMatrix(const void* data, int data_type, int32_t nrow,
   for (int c = 0; c < ncol; ++c) if (!all[c]->is_trivial()) used.push_back(c);
   if (used.empty()) Log::Warning("There are no meaningful features, as all feature values are constant.");
   std::vector<int> order = used;
+  std::vector<int> bundle_of_real(ncol, 0);
   if (config.enable_bundle && !used.empty()) {
-    order = BundledFeatureOrder(all, used, sample_vals, sample_idx, sample_cnt, nrow);
+    order = BundledFeatureOrder(all, used, sample_vals, sample_idx, sample_cnt, nrow, &bundle_of_real);
   }
   ds->real_to_inner_.assign(ncol, -1);
   for (int f : order) {
@@ -242,6 +246,7 @@ Dataset* Dataset::FromDenseMatrix(const void* data, int data_type, int32_t nrow,
     }
     ds->real_to_inner_[f] = static_cast<int>(ds->inner_to_real_.size());
     ds->inner_to_real_.push_back(f);
+    ds->bundle_of_.push_back(bundle_of_real[f]);
     ds->mappers_.push_back(all[f]);
   }
   for (int c = 0; c < ncol; ++c) ds->feature_names_.push_back("Column_" + std::to_string(c));
@@ -258,6 +263,8 @@ Dataset* Dataset::FromDenseMatrixAligned(const void* data, int data_type, int32_
   ds->num_total_features_ = ncol;
   ds->mappers_ = ref.mappers_;
   ds->inner_to_real_ = ref.inner_to_real_;
+  // (no bundles: Dataset::CreateValid, src/io/dataset.cpp:710-728, gives every feature of an aligned dataset a group of
+  // its own, so nothing is overwritten there)
   ds->real_to_inner_ = ref.real_to_inner_;
   ds->feature_names_ = ref.feature_names_;
   ds->BinAllRows(data, data_type, nrow, ncol, row_major, config.gpu_device_id);
@@ -290,7 +297,7 @@ void Dataset::BinAllRows(const void* data, int data_type, int32_t nrow, int32_t 
       const BinMapper& m = *mappers_[f];
       feats[f].column = inner_to_real_[f]; feats[f].num_bin = m.num_bin();
       feats[f].most_freq_bin = static_cast<int>(m.most_freq_bin()); feats[f].missing_type = m.missing_type();
-      feats[f].bound_offset = static_cast<int>(bounds.size()); feats[f].reserved = 0;
+      feats[f].bound_offset = static_cast<int>(bounds.size()); feats[f].bundle = bundle_of(f);
       bounds.insert(bounds.end(), m.upper_bounds().begin(), m.upper_bounds().end());
     }
     int dev = device >= 0 ? device : 0;
@@ -308,6 +315,14 @@ void Dataset::BinAllRows(const void* data, int data_type, int32_t nrow, int32_t 
   int FS = 0;
   for (int f = 0; f < F; ++f) { wide[f] = stored_values(f) > 256; scol[f] = FS; FS += wide[f] ? 2 : 1; }
   bins_.assign(static_cast<size_t>(nrow) * std::max(FS, 1), 0);
+  std::vector<std::vector<int>> bundles;
+  for (int f = 0; f < F; ++f) {
+    const int b = bundle_of(f);
+    if (b <= 0) continue;
+    if (static_cast<int>(bundles.size()) < b) bundles.resize(b);
+    bundles[b - 1].push_back(f);
+  }
+  for (auto& g : bundles) std::sort(g.begin(), g.end(), [&](int a, int b) { return inner_to_real_[a] > inner_to_real_[b]; });
 #pragma omp parallel for schedule(static)
   for (int32_t r = 0; r < nrow; ++r) {
     uint8_t* out = bins_.data() + static_cast<size_t>(r) * FS;
@@ -315,6 +330,15 @@ void Dataset::BinAllRows(const void* data, int data_type, int32_t nrow, int32_t 
       const uint32_t v = stored_value(f, M.at(r, inner_to_real_[f]));
       out[scol[f]] = static_cast<uint8_t>(v & 255u);
       if (wide[f]) out[scol[f] + 1] = static_cast<uint8_t>(v >> 8);
+    }
+    for (const auto& g : bundles) {   // members by descending raw column: the last push of the reference's row loop wins
+      bool seen = false;
+      for (int f : g) {
+        const int v = out[scol[f]] | (wide[f] ? out[scol[f] + 1] << 8 : 0);
+        if (v == 0) continue;
+        if (seen) { out[scol[f]] = 0; if (wide[f]) out[scol[f] + 1] = 0; }
+        seen = true;
+      }
     }
   }
   // the matrix only exists to be uploaded: page-lock it (a no-op without a device)

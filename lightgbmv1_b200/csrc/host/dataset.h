@@ -42,6 +42,7 @@ class Dataset {
   int num_storage_columns() const { int n = 0; for (int f = 0; f < num_features(); ++f) n += stored_values(f) > 256 ? 2 : 1; return n; }
   int num_total_features() const { return num_total_features_; }
   int real_feature_index(int inner) const { return inner_to_real_[inner]; }
+  int bundle_of(int inner) const { return bundle_of_.empty() ? 0 : bundle_of_[inner]; }
   int inner_feature_index(int real) const { return real_to_inner_[real]; }
   const BinMapper& mapper(int inner) const { return *mappers_[inner]; }
   // row-major [num_data][num_features] stored values on the HOST.  When the matrix was binned on the device it is
@@ -69,6 +70,9 @@ class Dataset {
   int num_total_features_ = 0;
   std::vector<std::shared_ptr<BinMapper>> mappers_;  // per inner feature
   std::vector<int> inner_to_real_, real_to_inner_;
+  // exclusive-feature bundle of every inner feature: 0 = none, b > 0 = the reference would keep it in one column with
+  // the other features of bundle b (dataset.cpp BundledFeatureOrder; the override rule is applied in BinAllRows)
+  std::vector<int> bundle_of_;
   mutable std::vector<uint8_t> bins_;
   mutable bool bins_pinned_ = false;  // page-locked for the upload (lgbcu_pin_host_buffer)
   LgbCuBinnedMatrix* dev_bins_ = nullptr;  // the matrix as binned on the device (lgbcu_bin_matrix), if it was

@@ -131,8 +131,11 @@ GBDT::GBDT(const Dataset* train, const Config& config)
       spec.kind = LGBCU_METRIC_MULTI_ERROR;
       spec.names = {config_.multi_error_top_k == 1 ? std::string("multi_error") : "multi_error@" + std::to_string(config_.multi_error_top_k)};
     }
+    else if (m == "mape") { spec.kind = LGBCU_METRIC_MAPE; spec.names = {"mape"}; }
+    else if (m == "cross_entropy") { spec.kind = LGBCU_METRIC_XENTROPY; spec.names = {"cross_entropy"}; }
+    else if (m == "kullback_leibler") { spec.kind = LGBCU_METRIC_XENTROPY; spec.names = {"kullback_leibler"}; spec.kl = true; }
     else if (m == "custom") continue;
-    else Log::Fatal("metric=%s is outside this library's path (l2, rmse, l1, huber, fair, poisson, gamma, tweedie, quantile, binary_logloss, binary_error, auc, ndcg, multi_logloss, multi_error)", m.c_str());
+    else Log::Fatal("metric=%s is outside this library's path (l2, rmse, l1, huber, fair, poisson, gamma, tweedie, quantile, mape, binary_logloss, binary_error, cross_entropy, kullback_leibler, auc, ndcg, multi_logloss, multi_error)", m.c_str());
     if ((spec.kind == LGBCU_METRIC_MULTI_LOGLOSS || spec.kind == LGBCU_METRIC_MULTI_ERROR) != (num_tree_per_iteration_ > 1))
       Log::Fatal("Multiclass objective and metrics don't match");
     metrics_.push_back(spec);
@@ -512,6 +515,19 @@ std::vector<std::string> GBDT::EvalNames() const {
   return out;
 }
 
+// The cross-entropy metrics divide by Common::ObtainMinMaxSum's sum of the weights (utils/common.h:843-883), which is
+// accumulated pairwise IN FLOAT; lgbcu_eval divides by the double sum.  Returns {float-accumulated sum, double sum}.
+static std::pair<double, double> XentWeightSums(const Metadata& md) {
+  const int n = static_cast<int>(md.weights.size());
+  const label_t* w = md.weights.data();
+  label_t sumw; int i;
+  if (n & 1) { sumw = w[0]; i = 2; } else { sumw = w[0] + w[1]; i = 3; }
+  for (; i < n; i += 2) sumw += w[i - 1] + w[i];
+  double exact = 0.0;
+  for (int k = 0; k < n; ++k) exact += w[k];
+  return {static_cast<double>(sumw), exact};
+}
+
 // GBDT::GetEvalAt (gbdt.cpp:545-565)
 std::vector<double> GBDT::GetEvalAt(int data_idx) {
   if (data_idx < 0 || data_idx > static_cast<int>(valid_.size())) Log::Fatal("Check failed: data_idx >= 0 && data_idx <= valid size");
@@ -525,15 +541,41 @@ std::vector<double> GBDT::GetEvalAt(int data_idx) {
     double buf[64];
     // metrics convert the raw score through the objective (ObjectiveFunction::ConvertOutput): a sigmoid for binary
     double sig = (objective_ && std::string(objective_->Name()) == "binary") ? config_.sigmoid : 0.0;
+    if (objective_ && std::string(objective_->Name()) == "cross_entropy") sig = 1.0;   // CrossEntropy::ConvertOutput
     if (m.kind == LGBCU_METRIC_QUANTILE || m.kind == LGBCU_METRIC_HUBER) sig = config_.alpha;
     if (m.kind == LGBCU_METRIC_FAIR) sig = config_.fair_c;
     if (m.kind == LGBCU_METRIC_TWEEDIE) sig = config_.tweedie_variance_power;
     if (m.kind == LGBCU_METRIC_MULTI_LOGLOSS) sig = objective_ ? 1.0 : 0.0;                                       // softmax first
     if (m.kind == LGBCU_METRIC_MULTI_ERROR) sig = (objective_ ? 1.0 : -1.0) * config_.multi_error_top_k;
     Check(lgbcu_eval(ctx_, set, m.kind, sig, buf, 64));
+    if (m.kind == LGBCU_METRIC_XENTROPY) {
+      const Metadata& md = data_idx == 0 ? train_->metadata() : valid_[data_idx - 1].data->metadata();
+      if (!md.weights.empty()) { const auto s = XentWeightSums(md); buf[0] *= s.second / s.first; }
+      if (m.kl) buf[0] += LabelEntropyOffset(data_idx);
+    }
     for (size_t i = 0; i < m.names.size(); ++i) ret.push_back(buf[i]);
   }
   return ret;
+}
+
+double GBDT::LabelEntropyOffset(int data_idx) {
+  if (static_cast<int>(kl_offset_.size()) <= data_idx) { kl_offset_.resize(data_idx + 1, 0.0); kl_offset_ready_.resize(data_idx + 1, 0); }
+  if (kl_offset_ready_[data_idx]) return kl_offset_[data_idx];
+  const Metadata& md = data_idx == 0 ? train_->metadata() : valid_[data_idx - 1].data->metadata();
+  const int n = static_cast<int>(md.label.size());
+  auto yent = [](double p) {   // YentLoss (xentropy_metric.hpp:60-67)
+    double hp = 0.0;
+    if (p > 0) hp += p * std::log(p);
+    const double q = 1.0f - p;
+    if (q > 0) hp += q * std::log(q);
+    return hp;
+  };
+  const double sum_w = md.weights.empty() ? static_cast<double>(n) : XentWeightSums(md).first;
+  double presum = 0.0f;
+  for (int i = 0; i < n; ++i) presum += md.weights.empty() ? yent(md.label[i]) : yent(md.label[i]) * md.weights[i];
+  kl_offset_[data_idx] = presum / sum_w;
+  kl_offset_ready_[data_idx] = 1;
+  return kl_offset_[data_idx];
 }
 
 void GBDT::GetValidScore(int idx, double* out, bool converted) const {

@@ -58,7 +58,10 @@ class GBDT {
   int64_t total_device_launches() const;
 
  private:
-  struct MetricSpec { int kind; std::vector<std::string> names; };
+  struct MetricSpec { int kind; std::vector<std::string> names; bool kl = false; };
+  // KullbackLeiblerDivergence's presummed label entropy (xentropy_metric.hpp:281-294) of the training set / a validation set
+  double LabelEntropyOffset(int data_idx);
+  std::vector<double> kl_offset_; std::vector<char> kl_offset_ready_;
   struct ValidEntry { const Dataset* data; int set; };
   void SetupNdcg(int set, const Metadata& md, int num_data);
   void AddTreeToValid(const Tree& tree);

@@ -196,6 +196,33 @@ class RegressionPercentile : public Objective {
   data_size_t num_data_ = 0; const label_t* label_ = nullptr; const label_t* weights_ = nullptr;
 };
 
+// RegressionMAPELOSS (src/objective/regression_objective.hpp:577-669): L1 with label_weight_ = 1 / max(1, |label|)
+class RegressionMAPE : public Objective {
+ public:
+  explicit RegressionMAPE(const Config& c) { if (c.reg_sqrt) Log::Fatal("reg_sqrt is outside this library's path"); }
+  void Init(const Metadata& meta, data_size_t n, const SumSync&) override {
+    num_data_ = n; label_ = meta.label.data();
+    if (meta.label.empty()) Log::Fatal("Label should not be NULL");
+    // with weights the reference calls the hessian constant although it holds the weights: not imitated
+    if (!meta.weights.empty()) Log::Fatal("objective=mape with weights is outside this library's path");
+    for (data_size_t i = 0; i < n; ++i) {
+      if (std::fabs(label_[i]) < 1) { Log::Warning("Met 'abs(label) < 1', will convert them to '1' in MAPE objective and metric"); break; }
+    }
+    label_weight_.resize(n);
+    for (data_size_t i = 0; i < n; ++i) label_weight_[i] = 1.0f / std::max(1.0f, std::fabs(label_[i]));
+  }
+  void Configure(LgbCuContext* ctx) const override { Check(lgbcu_set_objective(ctx, LGBCU_OBJ_MAPE, 0, 0, 0)); }
+  double BoostFromScore(int) const override { return LabelWeightedPercentile(label_, label_weight_.data(), num_data_, 0.5); }
+  bool IsRenewTreeOutput() const override { return true; }
+  double RenewAlpha() const override { return 0.5; }
+  bool RenewAlphaIsFloat() const override { return false; }
+  std::string ToString() const override { return "mape"; }
+  const char* Name() const override { return "mape"; }
+
+ private:
+  data_size_t num_data_ = 0; const label_t* label_ = nullptr; std::vector<label_t> label_weight_;
+};
+
 // src/objective/multiclass_objective.hpp (MulticlassSoftmax)
 class MulticlassSoftmax : public Objective {
  public:
@@ -300,6 +327,47 @@ class RegressionPointwise : public Objective {
   data_size_t num_data_ = 0; const label_t* label_ = nullptr; const label_t* weights_ = nullptr;
 };
 
+// src/objective/xentropy_objective.hpp:44-147 (CrossEntropy): labels are probabilities in [0, 1]
+class CrossEntropy : public Objective {
+ public:
+  explicit CrossEntropy(const Config&) {}
+  void Init(const Metadata& meta, data_size_t n, const SumSync&) override {
+    num_data_ = n; label_ = meta.label.data(); weights_ = meta.weights.empty() ? nullptr : meta.weights.data();
+    if (meta.label.empty()) Log::Fatal("Label should not be NULL");
+    for (data_size_t i = 0; i < n; ++i) {   // Common::CheckElementsIntervalClosed
+      if (!(label_[i] >= 0.0f && label_[i] <= 1.0f)) Log::Fatal("[%s]: does not tolerate element [#%d = %f] outside [0, 1]", Name(), i, label_[i]);
+    }
+    if (weights_) {
+      label_t minw = weights_[0]; double sumw = 0.0;
+      for (data_size_t i = 0; i < n; ++i) { minw = std::min(minw, weights_[i]); sumw += weights_[i]; }
+      if (minw < 0.0f) Log::Fatal("[%s]: at least one weight is negative", Name());
+      if (sumw == 0.0f) Log::Fatal("[%s]: sum of weights is zero", Name());
+    }
+  }
+  void Configure(LgbCuContext* ctx) const override { Check(lgbcu_set_objective(ctx, LGBCU_OBJ_XENTROPY, 0, 0, 0)); }
+  double BoostFromScore(int) const override {
+    double suml = 0.0f, sumw = 0.0f;
+    if (weights_) {
+#pragma omp parallel for schedule(static) reduction(+:suml, sumw)
+      for (data_size_t i = 0; i < num_data_; ++i) { suml += label_[i] * weights_[i]; sumw += weights_[i]; }
+    } else {
+      sumw = static_cast<double>(num_data_);
+#pragma omp parallel for schedule(static) reduction(+:suml)
+      for (data_size_t i = 0; i < num_data_; ++i) suml += label_[i];
+    }
+    double pavg = suml / sumw;
+    pavg = std::min(pavg, 1.0 - kEpsilon);
+    pavg = std::max<double>(pavg, kEpsilon);
+    return std::log(pavg / (1.0f - pavg));
+  }
+  void ConvertOutput(const double* in, double* out) const override { out[0] = 1.0f / (1.0f + std::exp(-in[0])); }
+  std::string ToString() const override { return Name(); }
+  const char* Name() const override { return "cross_entropy"; }
+
+ private:
+  data_size_t num_data_ = 0; const label_t* label_ = nullptr; const label_t* weights_ = nullptr;
+};
+
 // src/objective/multiclass_objective.hpp:186-276 (MulticlassOVA): one BinaryLogloss per class
 class MulticlassOVA : public Objective {
  public:
@@ -339,6 +407,8 @@ Objective* Objective::Create(const Config& c) {
   if (c.objective == "tweedie") return new RegressionPointwise(c, LGBCU_OBJ_TWEEDIE);
   if (c.objective == "regression_l1") return new RegressionPercentile(c, false);
   if (c.objective == "quantile") return new RegressionPercentile(c, true);
+  if (c.objective == "cross_entropy") return new CrossEntropy(c);
+  if (c.objective == "mape") return new RegressionMAPE(c);
   if (c.objective == "binary") return new BinaryLogloss(c);
   if (c.objective == "regression") return new RegressionL2(c);
   if (c.objective == "lambdarank") return new Lambdarank(c);

@@ -52,6 +52,18 @@ int ref_feature_stored_column(void* ds, int inner, uint8_t* out) {
   return 0;
 }
 
+// bin of every row in the FEATURE's space, as the split and the tree walk see it (BinIterator::Get: a stored value
+// outside the feature's range of a shared column reads as the most frequent bin), and the group of the feature
+int ref_feature_bin_column(void* ds, int inner, int32_t* out) {
+  const Dataset* d = reinterpret_cast<Dataset*>(ds);
+  std::unique_ptr<BinIterator> it(d->FeatureIterator(inner));
+  it->Reset(0);
+  for (data_size_t i = 0; i < d->num_data(); ++i) out[i] = static_cast<int32_t>(it->Get(i));
+  return 0;
+}
+int ref_feature_group(void* ds, int inner) { return reinterpret_cast<Dataset*>(ds)->Feature2Group(inner); }
+int ref_num_groups(void* ds) { return reinterpret_cast<Dataset*>(ds)->num_feature_groups(); }
+
 static Bin* make_dense(const uint8_t* stored, int n_total, int num_total_bin) {
   Bin* b = Bin::CreateDenseBin(n_total, num_total_bin);
   for (int i = 0; i < n_total; ++i) b->Push(0, i, stored[i]);

@@ -435,7 +435,7 @@ def test_errors_are_reported_not_fatal():
     with pytest.raises(N.LgbCuError):
         L.begin_tree()          # no dataset
     with pytest.raises(N.LgbCuError):
-        L.set_dataset(np.zeros((4, 1), np.uint8), [(300, 0, 0, 0)])   # > 8-bit bins
+        L.set_dataset(np.zeros((4, 2), np.uint8), [(70000, 0, 0, 0)])   # > 16-bit bins
     L.close()
 
 

@@ -336,3 +336,73 @@ def test_oracle_tree_matches_reference_tree(shim, orc, ref, pi):
         if abs(got) <= 1e-35:
             got = 0.0
         assert got == want, f"leaf {leaf}: {got!r} vs {want!r}"
+
+
+def sparse_matrix(seed, n, dtype=np.float32):
+    """One-hot blocks (exclusive by construction), sparse numeric columns that collide in a few rows, a column whose
+    most frequent value is not zero, and two dense columns: the reference bundles the sparse ones into shared columns."""
+    rng = np.random.default_rng(seed)
+    cols = []
+    for levels in (6, 9):
+        cat = rng.integers(0, levels, size=n)
+        block = [(cat == v).astype(np.float64) * (1.0 + 0.25 * v) for v in range(levels)]
+        for _ in range(2):                                 # two rows where a second member is set as well: a dense bundle
+            r = int(rng.integers(0, n))                    # tolerates n / 10000 such rows and keeps only the last pushed value
+            block[(int(cat[r]) + 1 + int(rng.integers(0, levels - 1))) % levels][r] = 1.0
+        cols += block
+    owner = rng.integers(0, 40, size=n)                    # sparse numeric columns on disjoint rows ...
+    sparse = [np.where(owner == k, rng.integers(1, 6, size=n).astype(np.float64), 0.0) for k in range(8)]
+    for k in range(0, 8, 2):                               # ... except one row per pair, where both are set: the bundle
+        r = int(rng.integers(0, n))                        # tolerates n / 10000 such rows and drops one of the two values
+        sparse[k][r] = 3.0; sparse[k + 1][r] = 2.0
+    cols += sparse
+    cols.append(np.where(rng.random(n) < 0.04, rng.standard_normal(n), 0.0))
+    cols.append(np.where(rng.random(n) < 0.97, 7.0, rng.integers(0, 4, size=n).astype(np.float64)))   # mfb != zero bin
+    cols.append(np.where(rng.random(n) < 0.02, np.nan, 0.0) + np.where(rng.random(n) < 0.03, 2.0, 0.0))
+    cols.append(rng.standard_normal(n))
+    cols.append(np.maximum(0, rng.standard_normal(n)))
+    X = np.stack(cols, axis=1).astype(dtype)
+    return X[:, rng.permutation(X.shape[1])]
+
+
+@pytest.mark.parametrize("seed,n,params", [(1, 30_000, "max_bin=255 verbosity=-1"),
+                                           (2, 42_000, "max_bin=63 min_data_in_bin=1 verbosity=-1"),
+                                           (3, 25_000, "max_bin=255 zero_as_missing=true verbosity=-1")])
+def test_bundled_features_bin_like_the_reference(shim, ref, ours, seed, n, params, monkeypatch):
+    # exclusive feature bundling: the reference shares one column between several sparse features, and rows where two of
+    # them are non-default lose all but the last pushed; this library keeps a column per feature and applies that rule
+    monkeypatch.setenv("LGBM_B200_HOST_BINNING", "1")
+    X = sparse_matrix(seed, n)
+    dr = ref.dataset_from_mat(X, params); do = ours.dataset_from_mat(X, params)
+    nf = shim.ref_num_inner_features(dr)
+    assert shim.ref_num_groups(dr) < nf, "the case does not bundle anything"
+    bins = np.empty((n, nf), dtype=np.int32); real = np.empty(nf, dtype=np.int32)
+    ours.check(ours.lib.LGBM_B200_DatasetDumpBins(do, bins.ctypes.data_as(C.POINTER(C.c_int32)), real.ctypes.data_as(C.POINTER(C.c_int32))))
+    lost = 0
+    for f in range(nf):
+        mr = (C.c_int32 * 5)(); br = (C.c_double * 300)()
+        shim.ref_feature_info(dr, C.c_int(f), mr, br, C.c_int(300))
+        assert mr[4] == real[f], "inner feature order"
+        want = np.empty(n, dtype=np.int32)
+        shim.ref_feature_bin_column(dr, C.c_int(f), want.ctypes.data_as(C.POINTER(C.c_int32)))
+        assert np.array_equal(bins[:, f], want), f"inner feature {f} (column {real[f]}): bins differ"
+    # the override must actually have happened somewhere: without it the matrices differ
+    do2 = ours.dataset_from_mat(X, params + " enable_bundle=false")
+    nf2 = C.c_int(); ours.check(ours.lib.LGBM_B200_DatasetNumInnerFeatures(do2, C.byref(nf2)))
+    bins2 = np.empty((n, nf2.value), dtype=np.int32); real2 = np.empty(nf2.value, dtype=np.int32)
+    ours.check(ours.lib.LGBM_B200_DatasetDumpBins(do2, bins2.ctypes.data_as(C.POINTER(C.c_int32)), real2.ctypes.data_as(C.POINTER(C.c_int32))))
+    by_real = {int(r): i for i, r in enumerate(real2)}
+    for f in range(nf):
+        lost += int(np.sum(bins[:, f] != bins2[:, by_real[int(real[f])]]))
+    assert lost > 0, "no conflicting row in the case: the override rule is not exercised"
+    # an aligned (validation) dataset is not bundled (Dataset::CreateValid): same bins as without bundling
+    Xv = sparse_matrix(seed, n + 5000)[n:]
+    dvr = ref.dataset_from_mat(Xv, params, reference=dr); dvo = ours.dataset_from_mat(Xv, params, reference=do)
+    assert shim.ref_num_groups(dvr) == nf
+    bv = np.empty((len(Xv), nf), dtype=np.int32)
+    ours.check(ours.lib.LGBM_B200_DatasetDumpBins(dvo, bv.ctypes.data_as(C.POINTER(C.c_int32)), real.ctypes.data_as(C.POINTER(C.c_int32))))
+    for f in range(nf):
+        want = np.empty(len(Xv), dtype=np.int32)
+        shim.ref_feature_bin_column(dvr, C.c_int(f), want.ctypes.data_as(C.POINTER(C.c_int32)))
+        assert np.array_equal(bv[:, f], want), f"validation data, inner feature {f}: bins differ"
+    ref.dataset_free(dr); ours.dataset_free(do); ours.dataset_free(do2)

@@ -65,3 +65,44 @@ def test_pointwise_regression_objectives_identical_trees(objective, weighted):
     np.testing.assert_allclose(ours.get_predict(bo, len(y)), ref.get_predict(br, len(y)), rtol=1e-9, atol=1e-9)
     assert ours.eval_names(bo) == ref.eval_names(br) == [name]
     np.testing.assert_allclose(ours.get_eval(bo, 0), ref.get_eval(br, 0), rtol=1e-9)
+
+
+@pytest.mark.parametrize("bagged", [False, True])
+def test_mape_identical_trees_and_leaf_values(bagged):
+    """RegressionMAPELOSS (regression_objective.hpp:577-669): L1 gradients scaled by 1 / max(1, |label|), and the same
+    weights in the leaf renewal's weighted median.  (With user weights it is refused: see lgbcu_get_gradients.)"""
+    X, y = make(40_000, 21)
+    y = (y * 3.0 + 4.0).astype(np.float32)     # labels on both sides of |label| = 1
+    params = ("objective=mape num_leaves=31 learning_rate=0.1 min_data_in_leaf=20 verbosity=-1 num_threads=4"
+              + (" bagging_fraction=0.6 bagging_freq=1 bagging_seed=9" if bagged else ""))
+    ref, ours, br, bo, nr, no = run_both(X, y, params, 10)
+    assert nr == no == 10
+    assert_same_model(ref, ours, br, bo)
+    np.testing.assert_allclose(ours.get_predict(bo, len(y)), ref.get_predict(br, len(y)), rtol=1e-9, atol=1e-9)
+    assert ours.eval_names(bo) == ref.eval_names(br) == ["mape"]
+    np.testing.assert_allclose(ours.get_eval(bo, 0), ref.get_eval(br, 0), rtol=1e-9)
+    with pytest.raises(Exception, match="mape"):
+        capi.train(ours, X, y, params, 1, weight=np.ones(len(y), dtype=np.float32))
+
+
+@pytest.mark.parametrize("weighted,metric", [(False, ""), (True, " metric=cross_entropy,kullback_leibler,binary_logloss")])
+def test_cross_entropy_identical_trees(weighted, metric):
+    """CrossEntropy (xentropy_objective.hpp:44-147): labels are probabilities in [0, 1]; cross_entropy and
+    kullback_leibler metrics (xentropy_metric.hpp) through the objective's sigmoid."""
+    X, _ = make(40_000, 31)
+    rng = np.random.default_rng(32)
+    p = 1.0 / (1.0 + np.exp(-(1.5 * X[:, 0] - X[:, 1] * X[:, 2] + 0.3 * rng.standard_normal(len(X)))))
+    y = np.where(rng.random(len(X)) < 0.3, (rng.random(len(X)) < p).astype(np.float64), p).astype(np.float32)   # hard and soft labels
+    w = (rng.random(len(y)).astype(np.float32) + 0.5) if weighted else None
+    params = f"objective=cross_entropy{metric} num_leaves=31 learning_rate=0.1 min_data_in_leaf=20 verbosity=-1 num_threads=4"
+    ref, ours, br, bo, nr, no = run_both(X, y, params, 10, weight=w)
+    assert nr == no == 10
+    assert_same_model(ref, ours, br, bo)
+    np.testing.assert_allclose(ours.get_predict(bo, len(y)), ref.get_predict(br, len(y)), rtol=1e-9, atol=1e-12)
+    assert ours.eval_names(bo) == ref.eval_names(br)
+    assert "cross_entropy" in ours.eval_names(bo)
+    np.testing.assert_allclose(ours.get_eval(bo, 0), ref.get_eval(br, 0), rtol=1e-9)
+    # the reference loads the model and converts with the same sigmoid
+    loaded = ref.load_model_from_string(ours.model_string(bo))
+    Xt, _ = make(3000, 33)
+    np.testing.assert_allclose(ours.predict_mat(bo, Xt), ref.predict_mat(loaded, Xt), rtol=0, atol=1e-12)
