@@ -52,6 +52,9 @@ enum { LGBCU_OBJ_NONE = 0, LGBCU_OBJ_BINARY = 1, LGBCU_OBJ_L2 = 2, LGBCU_OBJ_LAM
 /* histogram kernel selection (LGBCU_HIST_AUTO picks by leaf size) */
 enum { LGBCU_HIST_AUTO = 0, LGBCU_HIST_GLOBAL_ATOMIC = 1, LGBCU_HIST_WARP_PRIVATE = 2 };
 
+#define LGBCU_BIN_NUMERICAL 0
+#define LGBCU_BIN_CATEGORICAL 1
+
 /* Per inner feature meta: what FeatureMetainfo + BinMapper give the CPU path
  * (src/treelearner/feature_histogram.hpp:25-38,1110-1148; include/LightGBM/bin.h:85-215). */
 typedef struct LgbCuFeatureMeta {
@@ -60,7 +63,7 @@ typedef struct LgbCuFeatureMeta {
   int32_t default_bin;    /* BinMapper::GetDefaultBin() */
   int32_t missing_type;   /* LGBCU_MISSING_* */
   int32_t real_index;     /* Dataset::RealFeatureIndex(inner) -- used for the tie-break of SplitInfo::operator> */
-  int32_t reserved;
+  int32_t bin_type;       /* LGBCU_BIN_NUMERICAL (0) or LGBCU_BIN_CATEGORICAL (BinType, include/LightGBM/bin.h:24-27) */
   double  penalty;        /* feature_contri (FeatureMetainfo::penalty) */
 } LgbCuFeatureMeta;
 
@@ -153,6 +156,10 @@ typedef struct LgbCuBinFeature {
   int32_t most_freq_bin;
   int32_t missing_type;   /* LGBCU_MISSING_* */
   int32_t bound_offset;   /* first upper bound of this feature in upper_bounds */
+  int32_t num_categories; /* -1: numerical.  >= 0: categorical, and upper_bounds[bound_offset ..) holds the feature's
+                           * num_categories category values in ascending order followed by their bins (as doubles);
+                           * NaN, negative and unlisted values map to bin 0 (BinMapper::ValueToBin, bin.h:457-494) */
+  int32_t pad;
   int32_t bundle;         /* 0: a feature of its own.  b > 0: member of exclusive-feature bundle b (the reference's
                            * multi-feature FeatureGroup over ONE DenseBin, include/LightGBM/feature_group.h:32-50): in a
                            * row where several members are off their most-frequent bin, only the member with the
@@ -333,6 +340,17 @@ LGBCU_API int lgbcu_valid_add_const(LgbCuContext* ctx, int32_t set, double value
 LGBCU_API int lgbcu_valid_add_tree(LgbCuContext* ctx, int32_t set, int32_t num_leaves, const int32_t* split_feature_inner,
                                    const int32_t* threshold_bin, const int8_t* decision_type, const int32_t* left_child,
                                    const int32_t* right_child, const double* leaf_value);
+/* Categorical features (LgbCuFeatureMeta::bin_type = LGBCU_BIN_CATEGORICAL; at most 256 bins each).  A categorical
+ * split sends a SET of bins left (FeatureHistogram::FindBestThresholdCategoricalInner, feature_histogram.hpp:277-513;
+ * DenseBin::SplitCategorical, dense_bin.hpp:309-363).  In a split record of such a feature `threshold` is an index
+ * into the tree's bin sets (8 x 32-bit words each, bit b = bin b), read with lgbcu_tree_cat_sets after lgbcu_train_tree
+ * (out = NULL returns the count alone).
+ * For the tree walks (lgbcu_add_score_by_tree, lgbcu_valid_add_tree) a categorical node has decision_type bit 0 set and
+ * threshold_bin = the index of its set among those staged with lgbcu_set_tree_cat_sets. */
+LGBCU_API int lgbcu_set_cat_params(LgbCuContext* ctx, double cat_smooth, double cat_l2, int32_t max_cat_threshold,
+                                   int32_t min_data_per_group, int32_t max_cat_to_onehot);
+LGBCU_API int lgbcu_tree_cat_sets(LgbCuContext* ctx, uint32_t* out, int32_t cap_sets, int32_t* num_sets);
+LGBCU_API int lgbcu_set_tree_cat_sets(LgbCuContext* ctx, const uint32_t* sets, int32_t num_sets);
 LGBCU_API int lgbcu_valid_copy_score(LgbCuContext* ctx, int32_t set, double* out, int32_t n);
 
 /* metrics: Metric::Eval of src/metric/regression_metric.hpp (l2, rmse), binary_metric.hpp (binary_logloss, auc),

@@ -13,7 +13,7 @@ struct LgbCuBinnedMatrix {
                                  // feature, two (low byte first) per feature with more than 256 stored values
 };
 
-struct BinFeatDev { int column, num_bin, mfb, missing_type, bound_off, scol; };   // scol = (first) byte column of the output
+struct BinFeatDev { int column, num_bin, mfb, missing_type, bound_off, scol, num_cat, pad; };   // num_cat >= 0: categorical   // scol = (first) byte column of the output
 
 template <typename T>
 __global__ void __launch_bounds__(256) k_bin_rows(const T* __restrict__ x, long long rows, int ncol, int row_major, long long ld,
@@ -26,7 +26,21 @@ __global__ void __launch_bounds__(256) k_bin_rows(const T* __restrict__ x, long 
     const BinFeatDev d = feats[f];
     double value = (double)(row_major ? x[r * ncol + d.column] : x[(long long)d.column * ld + r]);
     int bin;
-    if (value != value && d.missing_type == LGBCU_MISSING_NAN) {
+    if (d.num_cat >= 0) {
+      // BinMapper::ValueToBin of a categorical feature (include/LightGBM/bin.h:457-460, 483-494): NaN, negative and unseen
+      // categories -> bin 0.  The feature's `bounds` hold its categories in ascending order, then their bins.
+      bin = 0;
+      if (value == value) {
+        // static_cast<int>(value): values outside the int range are undefined there; they are taken as unseen here
+        const int iv = (value > -2147483649.0 && value < 2147483648.0) ? (int)value : -1;
+        if (iv >= 0) {
+          const double* cats = bounds + d.bound_off;
+          int l = 0, rr = d.num_cat - 1;
+          while (l < rr) { const int m = (l + rr) >> 1; if (cats[m] < (double)iv) l = m + 1; else rr = m; }
+          if (d.num_cat > 0 && cats[l] == (double)iv) bin = (int)cats[d.num_cat + l];
+        }
+      }
+    } else if (value != value && d.missing_type == LGBCU_MISSING_NAN) {
       bin = d.num_bin - 1;
     } else {
       if (value != value) value = 0.0;
@@ -137,9 +151,10 @@ int lgbcu_bin_matrix(int device, const void* data, int data_type, int32_t nrow, 
   };
   std::vector<BinFeatDev> hf(num_features);
   for (int f = 0; f < num_features; ++f) {
+    const int ncat = feats[f].num_categories;   // < 0: numerical
     NEED(feats[f].column >= 0 && feats[f].column < ncol && feats[f].num_bin >= 1 && feats[f].bound_offset >= 0 &&
-         feats[f].bound_offset + feats[f].num_bin <= num_bounds, "lgbcu_bin_matrix: bad descriptor of feature %d", f);
-    hf[f] = BinFeatDev{feats[f].column, feats[f].num_bin, feats[f].most_freq_bin, feats[f].missing_type, feats[f].bound_offset, 0};
+         feats[f].bound_offset + (ncat >= 0 ? 2 * ncat : feats[f].num_bin) <= num_bounds, "lgbcu_bin_matrix: bad descriptor of feature %d", f);
+    hf[f] = BinFeatDev{feats[f].column, feats[f].num_bin, feats[f].most_freq_bin, feats[f].missing_type, feats[f].bound_offset, 0, ncat, 0};
   }
   int FS = 0;   // byte columns of the result
   for (int f = 0; f < num_features; ++f) { hf[f].scol = FS; FS += (hf[f].num_bin + (hf[f].mfb == 0 ? 0 : 1) > 256) ? 2 : 1; }

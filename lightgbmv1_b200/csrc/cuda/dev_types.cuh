@@ -30,8 +30,12 @@ struct DevFeat {
   // first.  `col` = the (first) byte column.  The matrices stay byte matrices, so the kernels of the 8-bit hot path are
   // untouched; data with a wide feature takes the general histogram and split-search paths.
   int col, wide;
+  // cat = 1: a categorical feature (BinType::CategoricalBin): bin 0 = NaN / negative / rare categories, a split sends a
+  // SET of bins left (a 256-bit set: categorical features are limited to 256 bins here)
+  int cat, pad_;
   double penalty;
 };
+#define LGB_CAT_WORDS 8   /* words of a categorical split's bin set */
 
 // stored value of feature F in a row-major row / in the column-major copy
 __device__ __forceinline__ int stored_bin_row(const uint8_t* __restrict__ row, const DevFeat& F) {
@@ -106,6 +110,8 @@ struct DevCtl {
   int kg, kh;        // fixed-point exponents
   double scale_g, scale_h, inv_g, inv_h;
   unsigned feat_done;  // "last block done" counter of k_find_split
+  int cat_count;       // entries of the categorical bin-set pool taken by the tree being grown
+  int cat_overflow;    // 1: the pool ran out (reported by lgbcu_train_tree)
   unsigned part_epoch[LGB_KMAX];  // per item: launches of k_partition so far (tags the words of V.part_sync); never reset
   unsigned bar_arrive[LGB_KMAX], bar_base[LGB_KMAX];  // k_partition, per item: blocks arrived so far (monotonic) / value when the launch began
   long long global_root;  // root rows over all ranks   } adjacent: one 2 x int64 sum all-reduce
@@ -128,6 +134,11 @@ struct DevCtl {
 // Feature ownership (data-parallel, wide data): what a rank sends to the all-gather per (leaf being expanded, child):
 // the best split over ITS features, with the key that SplitInfo::operator> compares.
 struct __align__(16) CandRec { DevSplit split; SplitKey key; };
+
+struct DevCatParams {   // Config: cat_smooth, cat_l2, max_cat_threshold, min_data_per_group, max_cat_to_onehot
+  double cat_smooth, cat_l2;
+  int max_cat_threshold, min_data_per_group, max_cat_to_onehot, pad;
+};
 
 struct DevParams {   // LgbCuTreeParams + derived switches
   int num_leaves, max_depth, min_data_in_leaf;
@@ -179,6 +190,11 @@ struct DevView {
   int part_sync_stride;
   unsigned* part_bits;       // partition scratch: 1 bit per row (1 = goes left)
   DevParams p;
+  // categorical splits: an append-only pool of bin sets per tree.  A categorical candidate takes the next entry
+  // (ctl->cat_count) and carries its index in DevSplit::threshold; partition, records and the host read the set there.
+  int any_cat, cat_cap;
+  unsigned* cat_pool;        // [cat_cap][LGB_CAT_WORDS]
+  DevCatParams cat;
 };
 
 #ifdef LGBCU_STAGE_TIMERS

@@ -215,6 +215,12 @@ struct LgbCuContext {
   // dataset
   int N = 0, F = 0, stride = 0, total_bin = 0, ntiles16 = 0;
   int FS = 0; bool any_wide = false;   // byte columns of the matrices; some feature has more than 256 stored values
+  // categorical features: `general` = the data takes the general split search / partition instantiations (wide or
+  // categorical feature present); the bin-set pool of the tree being grown; the sets staged for the tree walks
+  bool any_cat = false, general = false; int cat_features = 0;
+  unsigned* d_cat_pool = nullptr; int cat_cap = 0;
+  unsigned* d_tree_cat = nullptr; int tree_cat_count = 0, tree_cat_cap = 0;
+  DevCatParams cat_params{10.0, 10.0, 32, 100, 4, 0};
   uint8_t* d_bins = nullptr;
   DevFeat* d_feats = nullptr;
   std::vector<DevFeat> h_feats;
@@ -296,6 +302,7 @@ struct LgbCuContext {
     DevView V;
     V.num_data = N; V.num_features = F; V.row_stride = stride; V.total_bin = total_bin; V.num_tiles16 = ntiles16;
     V.num_storage = FS; V.any_wide = any_wide ? 1 : 0;
+    V.any_cat = any_cat ? 1 : 0; V.cat_cap = cat_cap; V.cat_pool = d_cat_pool; V.cat = cat_params;
     V.bins = d_bins; V.feats = d_feats; V.feat_used = d_feat_used; V.splittable = d_splittable;
     V.parent_split = d_parent_split; V.mfb_fix = d_mfb_fix; V.spec = d_spec; V.expanded = d_expanded; V.pool_slots = pool_slots;
     V.bits_stride = bits_stride; V.part_sync_stride = part_sync_stride;
@@ -361,6 +368,10 @@ int ensure_tree_buffers(LgbCuContext* c) {
   c->pool_slots = (int)slots;
   CU(dev_alloc(&c->d_pool, slots * c->total_bin));
   CU(dev_alloc(&c->d_splittable, slots * c->F));
+  if (c->any_cat) {   // every (categorical feature, child of an expansion) that finds a split takes one bin set
+    c->cat_cap = (int)std::min<size_t>((size_t)1 << 30, (size_t)c->cat_features * 2 * slots + 1);
+    CU(dev_alloc(&c->d_cat_pool, (size_t)c->cat_cap * LGB_CAT_WORDS));
+  }
   CU(dev_alloc(&c->d_mfb_fix, slots * c->F));
   CU(cudaMemsetAsync(c->d_mfb_fix, 0, sizeof(double2) * slots * c->F, c->stream));
   CU(dev_alloc(&c->d_leaves, (size_t)L));
@@ -407,7 +418,7 @@ int launch_partition(LgbCuContext* c, long long rows, int mode) {
   at[0].id = cudaLaunchAttributeCooperative;
   at[0].val.cooperative = 1;
   cfg.attrs = at; cfg.numAttrs = 1;
-  if (c->any_wide) CU(cudaLaunchKernelEx(&cfg, k_partition<true>, V, mode));
+  if (c->general) CU(cudaLaunchKernelEx(&cfg, k_partition<true>, V, mode));
   else CU(cudaLaunchKernelEx(&cfg, k_partition<false>, V, mode));
   g_launches.fetch_add(1, std::memory_order_relaxed);
   return 0;
@@ -579,7 +590,13 @@ int upload_tree(LgbCuContext* c, int32_t num_leaves, const int32_t* split_featur
     CU(dev_alloc(&c->d_tree_f64, (size_t)num_leaves));
     c->tree_cap = num_leaves;
   }
-  for (int i = 0; i < ni; ++i) NEED(split_feature_inner[i] >= 0 && split_feature_inner[i] < c->F, "add_score_by_tree: split feature out of range");
+  for (int i = 0; i < ni; ++i) {
+    NEED(split_feature_inner[i] >= 0 && split_feature_inner[i] < c->F, "add_score_by_tree: split feature out of range");
+    if (decision_type[i] & 1) {
+      NEED(threshold_bin[i] >= 0 && threshold_bin[i] < c->tree_cat_count, "add_score_by_tree: categorical node %d names set %d, %d were staged (lgbcu_set_tree_cat_sets)", i, threshold_bin[i], c->tree_cat_count);
+      NEED(c->h_feats[split_feature_inner[i]].cat, "add_score_by_tree: categorical node on the numerical feature %d", split_feature_inner[i]);
+    }
+  }
   int* d_feat = c->d_tree_i32, *d_thr = d_feat + num_leaves, *d_lc = d_thr + num_leaves, *d_rc = d_lc + num_leaves;
   CU(cudaMemcpyAsync(d_feat, split_feature_inner, sizeof(int) * ni, cudaMemcpyHostToDevice, c->stream));
   CU(cudaMemcpyAsync(d_thr, threshold_bin, sizeof(int) * ni, cudaMemcpyHostToDevice, c->stream));
@@ -588,7 +605,7 @@ int upload_tree(LgbCuContext* c, int32_t num_leaves, const int32_t* split_featur
   CU(cudaMemcpyAsync(c->d_tree_i8, decision_type, ni, cudaMemcpyHostToDevice, c->stream));
   CU(cudaMemcpyAsync(c->d_tree_f64, leaf_value, sizeof(double) * num_leaves, cudaMemcpyHostToDevice, c->stream));
   T->split_feature = d_feat; T->threshold_bin = d_thr; T->decision_type = c->d_tree_i8; T->left_child = d_lc; T->right_child = d_rc;
-  T->leaf_value = c->d_tree_f64; T->num_leaves = num_leaves;
+  T->leaf_value = c->d_tree_f64; T->num_leaves = num_leaves; T->cat_sets = c->d_tree_cat;
   return 0;
 }
 
@@ -704,6 +721,8 @@ int lgbcu_destroy(LgbCuContext* c) {
   xchg_teardown(c);
   lgbcu_comm_destroy(c);
   free_valid_sets(c);
+  if (c->d_cat_pool) { lgb_dev_free(c->d_cat_pool); c->d_cat_pool = nullptr; }
+  if (c->d_tree_cat) { lgb_dev_free(c->d_tree_cat); c->d_tree_cat = nullptr; }
   void* ptrs[] = {c->d_bins, c->d_feats, c->d_feat_used, c->d_grad_base, c->d_hess_base, c->d_gh, c->d_label, c->d_weight, c->d_score_base,
                   c->d_indices[0], c->d_indices[1], c->d_part_bits, c->d_part_sync, c->d_bins_col, c->d_query, c->d_label_gain,
                   c->d_inv_max_dcg, c->d_sigmoid_table, c->d_pool, c->d_splittable, c->d_leaves, c->d_best,
@@ -738,7 +757,7 @@ static int setup_dataset_common(LgbCuContext* c, int32_t num_data, int32_t num_f
   c->N = num_data; c->F = num_features;
   c->h_feats.resize(num_features);
   int base = 0, scol = 0;
-  c->any_wide = false;
+  c->any_wide = false; c->any_cat = false; c->cat_features = 0;
   for (int f = 0; f < num_features; ++f) {
     DevFeat& d = c->h_feats[f];
     const LgbCuFeatureMeta& m = meta[f];
@@ -749,13 +768,18 @@ static int setup_dataset_common(LgbCuContext* c, int32_t num_data, int32_t num_f
     NEED(d.nslots <= 65536, "lgbcu_set_dataset: feature %d needs %d stored values; at most 16-bit bins are supported", f, d.nslots);
     d.wide = d.nslots > 256 ? 1 : 0; d.col = scol; scol += d.wide ? 2 : 1;
     c->any_wide = c->any_wide || d.wide;
+    d.cat = m.bin_type == LGBCU_BIN_CATEGORICAL ? 1 : 0; d.pad_ = 0;
+    NEED(m.bin_type == LGBCU_BIN_NUMERICAL || m.bin_type == LGBCU_BIN_CATEGORICAL, "lgbcu_set_dataset: bad bin_type of feature %d", f);
+    NEED(!d.cat || d.num_bin <= 256, "lgbcu_set_dataset: the categorical feature %d has %d bins; at most 256 are supported", f, d.num_bin);
+    if (d.cat) { c->any_cat = true; c->cat_features += 1; }
     d.real_index = m.real_index; d.penalty = m.penalty;
     base += d.nslots;
   }
   {
-    const int fb = c->any_wide ? KEY_FEAT_BITS_WIDE : KEY_FEAT_BITS;
+    c->general = c->any_wide || c->any_cat;
+    const int fb = c->general ? KEY_FEAT_BITS_WIDE : KEY_FEAT_BITS;
     NEED(num_features < (1 << fb), "lgbcu_set_dataset: %d features exceed the supported %d%s", num_features, (1 << fb) - 1,
-         c->any_wide ? " (for data with more than 256 bins in a feature)" : "");
+         c->general ? " (for data with a categorical feature or more than 256 bins in a feature)" : "");
   }
   c->total_bin = base;
   c->FS = scol;
@@ -1113,6 +1137,46 @@ int lgbcu_add_score_by_partition(LgbCuContext* c, const double* leaf_value, int3
   return 0;
 }
 
+// Categorical splits.  Config's cat_smooth / cat_l2 / max_cat_threshold / min_data_per_group / max_cat_to_onehot
+// (feature_histogram.hpp:277-513 reads them through meta_->config)
+int lgbcu_set_cat_params(LgbCuContext* c, double cat_smooth, double cat_l2, int32_t max_cat_threshold, int32_t min_data_per_group,
+                         int32_t max_cat_to_onehot) {
+  NEED(c, "lgbcu: NULL context");
+  NEED(cat_smooth >= 0 && cat_l2 >= 0 && max_cat_threshold > 0 && min_data_per_group > 0 && max_cat_to_onehot > 0,
+       "lgbcu_set_cat_params: parameter out of range");
+  c->cat_params = DevCatParams{cat_smooth, cat_l2, max_cat_threshold, min_data_per_group, max_cat_to_onehot, 0};
+  drop_graph(c);   // the captured launches hold the parameters by value
+  return 0;
+}
+
+// The bin sets of the tree lgbcu_train_tree just grew: a categorical record's `threshold` is an index into them
+int lgbcu_tree_cat_sets(LgbCuContext* c, uint32_t* out, int32_t cap_sets, int32_t* num_sets) {
+  NEED(c && num_sets, "lgbcu_tree_cat_sets: NULL argument");
+  NEED(c->tree_begun && c->h_ctl, "lgbcu_tree_cat_sets: no tree has been grown");
+  const int n = c->any_cat ? c->h_ctl->cat_count : 0;
+  *num_sets = n;
+  if (n == 0 || out == nullptr) return 0;   // out = NULL: the count alone
+  NEED(cap_sets >= n, "lgbcu_tree_cat_sets: room for %d sets, the tree has %d", cap_sets, n);
+  USE_DEVICE(c->device);
+  CU(cudaMemcpyAsync(out, c->d_cat_pool, sizeof(unsigned) * LGB_CAT_WORDS * (size_t)n, cudaMemcpyDeviceToHost, c->stream));
+  CU(cudaStreamSynchronize(c->stream));
+  return 0;
+}
+
+// Stage the bin sets ([num_sets][8] words) that the categorical nodes of the trees passed to lgbcu_add_score_by_tree /
+// lgbcu_valid_add_tree from now on name in threshold_bin (Tree::cat_threshold_inner_, tree.h)
+int lgbcu_set_tree_cat_sets(LgbCuContext* c, const uint32_t* sets, int32_t num_sets) {
+  NEED(c && num_sets >= 0 && (sets || num_sets == 0), "lgbcu_set_tree_cat_sets: bad argument");
+  USE_DEVICE(c->device);
+  if (c->tree_cat_cap < num_sets) { CU(dev_alloc(&c->d_tree_cat, (size_t)num_sets * LGB_CAT_WORDS)); c->tree_cat_cap = num_sets; }
+  if (num_sets > 0) {
+    CU(cudaMemcpyAsync(c->d_tree_cat, sets, sizeof(unsigned) * LGB_CAT_WORDS * (size_t)num_sets, cudaMemcpyHostToDevice, c->stream));
+    CU(cudaStreamSynchronize(c->stream));
+  }
+  c->tree_cat_count = num_sets;
+  return 0;
+}
+
 int lgbcu_add_score_by_tree(LgbCuContext* c, int32_t num_leaves, const int32_t* split_feature_inner,
                             const int32_t* threshold_bin, const int8_t* decision_type, const int32_t* left_child,
                             const int32_t* right_child, const double* leaf_value, const int32_t* rows, int32_t num_rows,
@@ -1219,7 +1283,7 @@ int lgbcu_hist_build(LgbCuContext* c, int32_t leaf) {
 // k_find_split comes in two instantiations so that data without wide features runs the kernel without the wide search
 // in it (the 8-bit kernel sits at its register cap: the extra code cost 0.1 ms per iteration when it was one kernel)
 static void launch_find_split(LgbCuContext* c, dim3 grid, const DevView& V, int mode, int leaf) {
-  if (c->any_wide) LAUNCH(k_find_split<true>, grid, FS_THREADS, 0, c->stream, V, mode, leaf);
+  if (c->general) LAUNCH(k_find_split<true>, grid, FS_THREADS, 0, c->stream, V, mode, leaf);
   else LAUNCH(k_find_split<false>, grid, FS_THREADS, 0, c->stream, V, mode, leaf);
 }
 
@@ -1429,6 +1493,7 @@ int lgbcu_train_tree(LgbCuContext* c, LgbCuSplitRecord* records, int32_t* num_sp
   }
   c->last_used_rounds = c->h_ctl->round;
   NEED(!c->h_ctl->xchg_error, "lgbcu_train_tree: a peer's histograms did not arrive within the exchange time-out (is every rank training?)");
+  NEED(!c->h_ctl->cat_overflow, "lgbcu_train_tree: the pool of categorical bin sets (%d entries) ran out", c->cat_cap);
   NEED(c->h_ctl->done, "lgbcu_train_tree: tree not finished after %d rounds", round);
   const int n = c->h_ctl->num_splits;
   NEED(n >= 0 && n <= L - 1, "lgbcu_train_tree: corrupt split count %d", n);

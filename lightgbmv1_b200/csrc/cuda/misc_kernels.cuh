@@ -202,7 +202,7 @@ __global__ void k_prepare_tree(DevView V, int root_count, int root_identity, int
     c->num_leaves = 1; c->done = 0; c->smaller = 0; c->larger = -1;
     c->split_leaf = c->split_feature = c->split_threshold = 0;
     c->split_default_left = 0; c->split_right_leaf = 1; c->split_left_count = 0;
-    c->num_splits = 0; c->feat_done = 0;
+    c->num_splits = 0; c->feat_done = 0; c->cat_count = 0; c->cat_overflow = 0;
     c->round = 0; c->num_items = 0; c->lookahead = lookahead;
     c->root_identity = root_identity; c->num_data = root_count;
     c->kg = fixed_exponent(c->max_g_bits, scale_rows);
@@ -367,6 +367,7 @@ struct TreeDev {
   const int* split_feature; const int* threshold_bin; const signed char* decision_type;
   const int* left_child; const int* right_child; const double* leaf_value;
   int num_leaves;
+  const unsigned* cat_sets;   // [num_cat][LGB_CAT_WORDS] bin sets of the categorical nodes (threshold_bin = index), or NULL
 };
 #define TREE_SMEM_NODES 1024
 __global__ void __launch_bounds__(256) k_add_score_tree(DevView V, TreeDev T, const int* __restrict__ rows, int n,
@@ -399,7 +400,9 @@ __global__ void __launch_bounds__(256) k_add_score_tree(DevView V, TreeDev T, co
       const int bin = stored == 0 ? F.mfb : stored - 1 + F.offset;
       const int missing_type = (dt[node] >> 2) & 3;
       bool left;
-      if ((missing_type == LGBCU_MISSING_ZERO && bin == F.default_bin) ||
+      if (dt[node] & 1) {   // Tree::CategoricalDecisionInner (tree.h:330-341): left = the bin is in the node's set
+        left = ((T.cat_sets[(size_t)thr[node] * LGB_CAT_WORDS + (bin >> 5)] >> (bin & 31)) & 1u) != 0;
+      } else if ((missing_type == LGBCU_MISSING_ZERO && bin == F.default_bin) ||
           (missing_type == LGBCU_MISSING_NAN && bin == F.num_bin - 1)) {
         left = (dt[node] & 2) != 0;
       } else {

@@ -117,7 +117,127 @@ __device__ void wide_find_best_threshold(const WideData& D, const DevFeat& F, co
   *splittable_out = splittable;
 }
 
-// The wide counterpart of find_item: same inputs, same outputs, any number of bins.  All FS_THREADS threads call.
+
+// ---- categorical features -------------------------------------------------------------------------------------------
+// FeatureHistogram::FindBestThresholdCategoricalInner (feature_histogram.hpp:277-513; no monotone constraints, no
+// extra_trees) by ONE thread, reading data_[t] through WideData.  One-hot (num_bin <= max_cat_to_onehot): every bin
+// against the rest.  Otherwise: the bins with enough data, stably sorted by sum_gradient / (sum_hessian + cat_smooth),
+// are accumulated from the low end and from the high end, up to max_cat_threshold bins a side.  `sorted` = scratch in
+// shared memory for 256 bin indices; `bits` = LGB_CAT_WORDS words that receive the set of BINS going left.
+__device__ void cat_find_best_threshold(const WideData& D, const DevFeat& F, const DevParams& P0, const DevCatParams& C,
+                                        double sum_g, double leaf_sum_h, int num_data, double parent_output,
+                                        unsigned char* sorted, double* ctr, unsigned* bits, DevSplit* out, int* splittable_out) {
+  DevSplit o;
+  o.gain = LGB_MIN_SCORE; o.feature = -1; o.real_feature = -1; o.threshold = 0; o.default_left = 0;
+  o.left_count = 0; o.right_count = 0; o.left_output = 0; o.right_output = 0;
+  o.left_sum_g = 0; o.left_sum_h = 0; o.right_sum_g = 0; o.right_sum_h = 0;
+  const double sum_h = leaf_sum_h + (double)(2 * 1e-15f);
+  double best_gain = LGB_MIN_SCORE, best_lg = 0, best_lh = 0;
+  int best_lc = 0;
+  double gain_shift;
+  if (P0.use_smoothing) {
+    const double sg = P0.use_l1 ? threshold_l1(sum_g, P0.lambda_l1) : sum_g;   // GetLeafGainGivenOutput
+    gain_shift = -(2.0 * sg * parent_output + (sum_h + P0.lambda_l2) * parent_output * parent_output);
+  } else {
+    gain_shift = leaf_gain(sum_g, sum_h, P0, num_data, 0.0);
+  }
+  const double min_gain_shift = gain_shift + P0.min_gain_to_split;
+  const int offset = F.offset;
+  const int bin_start = 1 - offset, bin_end = F.num_bin - offset;
+  int used_bin = -1;
+  DevParams P = P0;   // l2 grows by cat_l2 in the many-vs-many search
+  const bool use_onehot = F.num_bin <= C.max_cat_to_onehot;
+  int best_threshold = -1, best_dir = 1;
+  const double cnt_factor = num_data / sum_h;
+  int splittable = 0;
+  if (use_onehot) {
+    for (int t = bin_start; t < bin_end; ++t) {
+      const double grad = D.g(t), hess = D.hh(t);
+      const int cnt = round_int(hess * cnt_factor);
+      if (cnt < P.min_data_in_leaf || hess < P.min_sum_hessian) continue;
+      const int other_count = num_data - cnt;
+      if (other_count < P.min_data_in_leaf) continue;
+      const double sum_other_h = sum_h - hess - LGB_EPS;
+      if (sum_other_h < P.min_sum_hessian) continue;
+      const double sum_other_g = sum_g - grad;
+      const double gain = leaf_gain(sum_other_g, sum_other_h, P, other_count, parent_output) +
+                          leaf_gain(grad, hess + LGB_EPS, P, cnt, parent_output);
+      if (gain <= min_gain_shift) continue;
+      splittable = 1;
+      if (gain > best_gain) { best_threshold = t; best_lg = grad; best_lh = hess + LGB_EPS; best_lc = cnt; best_gain = gain; }
+    }
+  } else {
+    used_bin = 0;
+    for (int i = bin_start; i < bin_end; ++i) {
+      if (round_int(D.hh(i) * cnt_factor) >= C.cat_smooth) {
+        sorted[used_bin] = (unsigned char)i;
+        ctr[used_bin] = D.g(i) / (D.hh(i) + C.cat_smooth);
+        ++used_bin;
+      }
+    }
+    P.lambda_l2 += C.cat_l2;
+    // std::stable_sort by ctr ascending: an insertion sort is stable and the list is short (<= 255)
+    for (int i = 1; i < used_bin; ++i) {
+      const unsigned char bi = sorted[i]; const double ci = ctr[i];
+      int j = i - 1;
+      while (j >= 0 && ci < ctr[j]) { sorted[j + 1] = sorted[j]; ctr[j + 1] = ctr[j]; --j; }
+      sorted[j + 1] = bi; ctr[j + 1] = ci;
+    }
+    const int max_num_cat = min(C.max_cat_threshold, (used_bin + 1) / 2);
+    for (int pass = 0; pass < 2; ++pass) {
+      const int dir = pass == 0 ? 1 : -1;
+      int start_pos = pass == 0 ? 0 : used_bin - 1;
+      int cnt_cur_group = 0, left_count = 0;
+      double lg = 0.0f, lh = LGB_EPS;
+      for (int i = 0; i < used_bin && i < max_num_cat; ++i) {
+        const int t = sorted[start_pos];
+        start_pos += dir;
+        const double grad = D.g(t), hess = D.hh(t);
+        const int cnt = round_int(hess * cnt_factor);
+        lg += grad; lh += hess; left_count += cnt; cnt_cur_group += cnt;
+        if (left_count < P.min_data_in_leaf || lh < P.min_sum_hessian) continue;
+        const int right_count = num_data - left_count;
+        if (right_count < P.min_data_in_leaf || right_count < C.min_data_per_group) break;
+        const double rh = sum_h - lh;
+        if (rh < P.min_sum_hessian) break;
+        if (cnt_cur_group < C.min_data_per_group) continue;
+        cnt_cur_group = 0;
+        const double rg = sum_g - lg;
+        const double gain = leaf_gain(lg, lh, P, left_count, parent_output) + leaf_gain(rg, rh, P, right_count, parent_output);
+        if (gain <= min_gain_shift) continue;
+        splittable = 1;
+        if (gain > best_gain) { best_lc = left_count; best_lg = lg; best_lh = lh; best_threshold = i; best_gain = gain; best_dir = dir; }
+      }
+    }
+  }
+  for (int w = 0; w < LGB_CAT_WORDS; ++w) bits[w] = 0u;
+  if (splittable) {
+    o.left_output = leaf_output(best_lg, best_lh, P, best_lc, parent_output);
+    o.left_count = best_lc;
+    o.left_sum_g = best_lg;
+    o.left_sum_h = best_lh - LGB_EPS;
+    o.right_output = leaf_output(sum_g - best_lg, sum_h - best_lh, P, num_data - best_lc, parent_output);
+    o.right_count = num_data - best_lc;
+    o.right_sum_g = sum_g - best_lg;
+    o.right_sum_h = sum_h - best_lh - LGB_EPS;
+    o.gain = best_gain - min_gain_shift;
+    if (use_onehot) {
+      const int b = best_threshold + offset;
+      bits[b >> 5] |= 1u << (b & 31);
+    } else {
+      for (int i = 0; i <= best_threshold; ++i) {
+        const int b = (best_dir == 1 ? sorted[i] : sorted[used_bin - 1 - i]) + offset;
+        bits[b >> 5] |= 1u << (b & 31);
+      }
+    }
+  }
+  o.gain *= F.penalty;
+  *out = o;
+  *splittable_out = splittable;
+}
+
+// The general counterpart of find_item: same inputs, same outputs, any number of bins, numerical or categorical.  All
+// FS_THREADS threads call.
 __device__ void find_item_wide(const DevView& V, ScanSmem& S, int f, int sel, const FindTarget& T, const DevFeat& F, bool used) {
   DevCtl* c = V.ctl;
   const int tid = threadIdx.x;
@@ -128,6 +248,8 @@ __device__ void find_item_wide(const DevView& V, ScanSmem& S, int f, int sel, co
   HistEntry* hs = V.pool + (size_t)Ls.slot * V.total_bin + F.hist_base;   // smaller leaf
   HistEntry* ht = V.pool + (size_t)Lt.slot * V.total_bin + F.hist_base;   // scanned leaf (sel 1: holds the parent)
   __shared__ double s_fix[2];
+  __shared__ unsigned char s_sorted[256];
+  __shared__ double s_ctr[256];
   DevSplit o; int sp = 0;
   o.gain = LGB_MIN_SCORE; o.feature = -1; o.real_feature = -1;
   if (used) {
@@ -179,7 +301,22 @@ __device__ void find_item_wide(const DevView& V, ScanSmem& S, int f, int sel, co
     if (tid == 0) {
       WideData D; D.h = ht; D.mfb = F.mfb > 0 ? F.mfb : -1000; D.fix_g = s_fix[0]; D.fix_h = s_fix[1]; D.inv_g = inv_g; D.inv_h = inv_h;
       const bool id0 = sel == 0 ? T.smaller_id0 : T.larger_id0;
-      wide_find_best_threshold(D, F, V.p, Lt.sum_g, Lt.sum_h, Lt.gcount, parent_output_of(Lt, id0 ? 0 : 1, V.p), &o, &sp);
+      const double parent_output = parent_output_of(Lt, id0 ? 0 : 1, V.p);
+      if (F.cat) {
+        unsigned bits[LGB_CAT_WORDS];
+        cat_find_best_threshold(D, F, V.p, V.cat, Lt.sum_g, Lt.sum_h, Lt.gcount, parent_output, s_sorted, s_ctr, bits, &o, &sp);
+        if (sp) {   // the set of bins going left takes the next pool entry; the split carries its index as "threshold"
+          const int e = atomicAdd(&c->cat_count, 1);
+          if (e < V.cat_cap) {
+            for (int w = 0; w < LGB_CAT_WORDS; ++w) V.cat_pool[(size_t)e * LGB_CAT_WORDS + w] = bits[w];
+            o.threshold = e;
+          } else {
+            c->cat_overflow = 1; o.gain = LGB_MIN_SCORE; sp = 0;
+          }
+        }
+      } else {
+        wide_find_best_threshold(D, F, V.p, Lt.sum_g, Lt.sum_h, Lt.gcount, parent_output, &o, &sp);
+      }
       o.feature = f; o.real_feature = F.real_index;
     }
   }
@@ -187,7 +324,7 @@ __device__ void find_item_wide(const DevView& V, ScanSmem& S, int f, int sel, co
     const size_t row = (size_t)(T.slot + sel) * V.num_features + f;
     V.feat_best[row] = o;
     SplitKey k; k.gain = o.gain; k.real_feature = o.real_feature;
-    k.pad = o.feature >= 0 ? key_pack<true>(o.feature, o.threshold, o.default_left) : 0;
+    k.pad = o.feature >= 0 ? key_pack<true>(o.feature, F.cat ? 0 : o.threshold, o.default_left) : 0;
     V.feat_key[row] = k;
     if (sel == 0 || used) V.splittable[(size_t)Lt.slot * V.num_features + f] = (int8_t)sp;
   }

@@ -154,7 +154,8 @@ void SortDoubles(std::vector<double>* values) {
 }  // namespace
 
 void BinMapper::FindBin(std::vector<double> values, size_t total_sample_cnt, int max_bin, int min_data_in_bin,
-                        int min_split_data, bool pre_filter, bool use_missing, bool zero_as_missing) {
+                        int min_split_data, bool pre_filter, bool use_missing, bool zero_as_missing, bool categorical) {
+  categorical_ = categorical;
   int num_sample = static_cast<int>(values.size());
   // drop NaNs, remember how many
   int kept = 0;
@@ -190,6 +191,57 @@ void BinMapper::FindBin(std::vector<double> values, size_t total_sample_cnt, int
   max_val_ = dv.back();
   const int nd = static_cast<int>(dv.size());
 
+  std::vector<int> cnt_in_bin;
+  if (categorical_) {
+    // src/io/bin.cpp:424-494: categories as ints (negative = NaN), by descending count; categories are kept until 99 % of
+    // the rows are covered AND max_bin bins exist (the reference's loop condition is an OR), rare ones share bin 0
+    std::vector<int> dvi, dci;
+    for (int i = 0; i < nd; ++i) {
+      const int val = static_cast<int>(dv[i]);
+      if (val < 0) { na_cnt += dc[i]; Log::Warning("Met negative value in categorical features, will convert it to NaN"); }
+      else if (dvi.empty() || val != dvi.back()) { dvi.push_back(val); dci.push_back(dc[i]); }
+      else dci.back() += dc[i];
+    }
+    upper_.clear(); bin_2_cat_.clear(); cat_2_bin_.clear();
+    num_bin_ = 0;
+    const int rest_cnt = static_cast<int>(total_sample_cnt - na_cnt);
+    if (rest_cnt > 0) {
+      if (dvi.back() / 100 > static_cast<int>(dvi.size()))
+        Log::Warning("Met categorical feature which contains sparse values. Consider renumbering to consecutive integers started from zero");
+      std::vector<std::pair<int, int>> arr;   // Common::SortForPair(counts, values, 0, true): stable, by count descending
+      for (size_t i = 0; i < dvi.size(); ++i) arr.emplace_back(dci[i], dvi[i]);
+      std::stable_sort(arr.begin(), arr.end(), [](const std::pair<int, int>& a, const std::pair<int, int>& b) { return a.first > b.first; });
+      const int cut_cnt = static_cast<int>(static_cast<double>((total_sample_cnt - na_cnt) * 0.99f) + 0.5f);   // RoundInt of a float product
+      size_t cur_cat = 0;
+      int used_cnt = 0;
+      int distinct_cnt = static_cast<int>(arr.size());
+      if (na_cnt > 0) ++distinct_cnt;
+      max_bin = std::min(distinct_cnt, max_bin);
+      bin_2_cat_.push_back(-1); cat_2_bin_[-1] = 0; cnt_in_bin.push_back(0);   // the dummy bin for NaN
+      num_bin_ = 1;
+      while (cur_cat < arr.size() && (used_cnt < cut_cnt || num_bin_ < max_bin)) {
+        if (arr[cur_cat].first < min_data_in_bin && cur_cat > 1) break;
+        bin_2_cat_.push_back(arr[cur_cat].second);
+        cat_2_bin_[arr[cur_cat].second] = static_cast<uint32_t>(num_bin_);
+        used_cnt += arr[cur_cat].first;
+        cnt_in_bin.push_back(arr[cur_cat].first);
+        ++num_bin_;
+        ++cur_cat;
+      }
+      missing_type_ = (cur_cat == arr.size() && na_cnt == 0) ? kMissingNone : kMissingNaN;
+      cnt_in_bin[0] = static_cast<int>(total_sample_cnt - used_cnt);
+    }
+    trivial_ = num_bin_ <= 1;
+    // NeedFilter, categorical branch (bin.cpp:63-73): only a two-bin feature can be filtered
+    if (!trivial_ && pre_filter && cnt_in_bin.size() <= 2) {
+      bool useful = false;
+      for (size_t i = 0; i + 1 < cnt_in_bin.size(); ++i) {
+        const int left = cnt_in_bin[i];
+        if (left >= min_split_data && static_cast<int>(total_sample_cnt) - left >= min_split_data) useful = true;
+      }
+      if (!useful) trivial_ = true;
+    }
+  } else {
   if (missing_type_ == kMissingZero) {
     upper_ = BoundsWithZeroBin(dv.data(), dc.data(), nd, max_bin, total_sample_cnt, min_data_in_bin);
     if (upper_.size() == 2) missing_type_ = kMissingNone;
@@ -203,7 +255,7 @@ void BinMapper::FindBin(std::vector<double> values, size_t total_sample_cnt, int
     upper_.push_back(static_cast<double>(kMissingNaN));
   }
   num_bin_ = static_cast<int>(upper_.size());
-  std::vector<int> cnt_in_bin(num_bin_, 0);
+  cnt_in_bin.assign(num_bin_, 0);
   {
     int b = 0;
     for (int i = 0; i < nd; ++i) {
@@ -216,6 +268,7 @@ void BinMapper::FindBin(std::vector<double> values, size_t total_sample_cnt, int
 
   trivial_ = num_bin_ <= 1;
   if (!trivial_ && pre_filter && NoUsefulSplit(cnt_in_bin, static_cast<int>(total_sample_cnt), min_split_data)) trivial_ = true;
+  }
   if (!trivial_) {
     default_bin_ = ValueToBin(0);
     // ArrayArgs<int>::ArgMax: first maximum
@@ -229,6 +282,15 @@ void BinMapper::FindBin(std::vector<double> values, size_t total_sample_cnt, int
 }
 
 uint32_t BinMapper::ValueToBin(double value) const {
+  if (categorical_) {   // bin.h:457-460, 483-494
+    if (std::isnan(value)) return 0;
+    // (the reference casts whatever it gets; a value outside the int range is undefined there and "unseen" here)
+    if (!(value > -2147483649.0 && value < 2147483648.0)) return 0;
+    const int iv = static_cast<int>(value);
+    if (iv < 0) return 0;
+    const auto it = cat_2_bin_.find(iv);
+    return it == cat_2_bin_.end() ? 0 : it->second;
+  }
   if (std::isnan(value)) {
     if (missing_type_ == kMissingNaN) return num_bin_ - 1;
     value = 0.0f;
@@ -244,6 +306,11 @@ uint32_t BinMapper::ValueToBin(double value) const {
 }
 
 std::string BinMapper::info_string() const {
+  if (categorical_) {   // Common::Join(bin_2_categorical_, ":")
+    std::ostringstream c;
+    for (size_t i = 0; i < bin_2_cat_.size(); ++i) { if (i) c << ':'; c << bin_2_cat_[i]; }
+    return c.str();
+  }
   std::ostringstream o;
   o << std::setprecision(std::numeric_limits<double>::digits10 + 2) << '[' << min_val_ << ':' << max_val_ << ']';
   return o.str();

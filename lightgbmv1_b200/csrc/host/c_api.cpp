@@ -635,7 +635,7 @@ int LGBM_B200_DatasetFeatureInfo(DatasetHandle handle, int inner_feature, int32_
   const BinMapper& m = ds->mapper(inner_feature);
   meta5[0] = m.num_bin(); meta5[1] = static_cast<int>(m.most_freq_bin()); meta5[2] = static_cast<int>(m.default_bin());
   meta5[3] = m.missing_type(); meta5[4] = ds->real_feature_index(inner_feature);
-  for (int i = 0; i < m.num_bin() && i < cap; ++i) upper_bounds[i] = m.upper_bounds()[i];
+  for (int i = 0; i < m.num_bin() && i < cap; ++i) upper_bounds[i] = m.BinToValue(i);   // categorical: the bin's category
   API_END();
 }
 

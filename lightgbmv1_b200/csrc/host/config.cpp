@@ -42,6 +42,7 @@ const std::unordered_map<std::string, std::string>& Aliases() {
       {"map_eval_at", "eval_at"}, {"map_at", "eval_at"}, {"num_machine", "num_machines"},
       {"feature_contrib", "feature_contri"}, {"fc", "feature_contri"}, {"fp", "feature_contri"}, {"feature_penalty", "feature_contri"},
       {"num_classes", "num_class"},
+      {"cat_feature", "categorical_feature"}, {"categorical_column", "categorical_feature"}, {"cat_column", "categorical_feature"},
   };
   return t;
 }
@@ -249,6 +250,26 @@ void Config::Set(const std::unordered_map<std::string, std::string>& p) {
   GetDouble(p, "alpha", &alpha);
   GetDouble(p, "fair_c", &fair_c);
   GetDouble(p, "poisson_max_delta_step", &poisson_max_delta_step);
+  if (GetStr(p, "categorical_feature", &s) && !s.empty()) {   // DatasetLoader::SetHeader (dataset_loader.cpp:142-164)
+    if (s.rfind("name:", 0) == 0) Log::Fatal("categorical_feature by column name needs a data file with a header; pass column indices");
+    categorical_feature.clear();
+    for (auto& t : SplitAny(s, ",")) {
+      char* end = nullptr;
+      const long v = std::strtol(t.c_str(), &end, 10);
+      if (end == t.c_str() || *end != 0) Log::Fatal("categorical_feature is not a number,\nif you want to use a column name,\nplease add the prefix \"name:\" to the column name");
+      categorical_feature.push_back(static_cast<int>(v));
+    }
+  }
+  GetInt(p, "min_data_per_group", &min_data_per_group);
+  GetInt(p, "max_cat_threshold", &max_cat_threshold);
+  GetInt(p, "max_cat_to_onehot", &max_cat_to_onehot);
+  GetDouble(p, "cat_l2", &cat_l2);
+  GetDouble(p, "cat_smooth", &cat_smooth);
+  if (min_data_per_group <= 0) Log::Fatal("min_data_per_group should be > 0");
+  if (max_cat_threshold <= 0) Log::Fatal("max_cat_threshold should be > 0");
+  if (max_cat_to_onehot <= 0) Log::Fatal("max_cat_to_onehot should be > 0");
+  if (cat_l2 < 0.0) Log::Fatal("cat_l2 should be >= 0");
+  if (cat_smooth < 0.0) Log::Fatal("cat_smooth should be >= 0");
   GetDouble(p, "tweedie_variance_power", &tweedie_variance_power);
   if (tweedie_variance_power < 1.0 || tweedie_variance_power >= 2.0) Log::Fatal("tweedie_variance_power should be in [1, 2)");
   if (fair_c <= 0.0) Log::Fatal("fair_c should be > 0");
@@ -298,7 +319,7 @@ void Config::Set(const std::unordered_map<std::string, std::string>& p) {
   if (neg_bagging_fraction <= 0.0 || neg_bagging_fraction > 1.0) Log::Fatal("neg_bagging_fraction should be in (0, 1]");
   for (const char* k : {"monotone_constraints", "forcedsplits_filename", "forcedbins_filename", "interaction_constraints",
                         "cegb_penalty_feature_lazy", "cegb_penalty_feature_coupled", "max_bin_by_feature",
-                        "categorical_feature", "linear_tree"}) {
+                        "linear_tree"}) {
     if (GetStr(p, k, &s)) Log::Fatal("parameter %s is outside this library's path", k);
   }
   Log::level() = verbosity;

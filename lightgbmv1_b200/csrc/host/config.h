@@ -57,6 +57,10 @@ struct Config {
   double sigmoid = 1.0;
   double alpha = 0.9;   // huber / quantile objectives and metrics (config.h:815)
   double fair_c = 1.0, poisson_max_delta_step = 0.7, tweedie_variance_power = 1.5;
+  // categorical features: raw column indices (config.h categorical_feature; "name:" lists need a data file's header)
+  std::vector<int> categorical_feature;
+  int min_data_per_group = 100, max_cat_threshold = 32, max_cat_to_onehot = 4;
+  double cat_l2 = 10.0, cat_smooth = 10.0;
   bool is_unbalance = false;
   double scale_pos_weight = 1.0;
   bool boost_from_average = true;

@@ -227,8 +227,9 @@ Dataset* Dataset::FromDenseMatrix(const void* data, int data_type, int32_t nrow,
 #pragma omp parallel for schedule(guided)
   for (int c = 0; c < ncol; ++c) {
     all[c].reset(new BinMapper());
+    const bool categorical = std::find(config.categorical_feature.begin(), config.categorical_feature.end(), c) != config.categorical_feature.end();
     all[c]->FindBin(sample_vals[c], static_cast<size_t>(sample_cnt), config.max_bin, config.min_data_in_bin, filter_cnt,
-                    config.feature_pre_filter, config.use_missing, config.zero_as_missing);
+                    config.feature_pre_filter, config.use_missing, config.zero_as_missing, categorical);
   }
   st.tick("FindBin");
   std::vector<int> used;
@@ -298,6 +299,16 @@ void Dataset::BinAllRows(const void* data, int data_type, int32_t nrow, int32_t 
       feats[f].column = inner_to_real_[f]; feats[f].num_bin = m.num_bin();
       feats[f].most_freq_bin = static_cast<int>(m.most_freq_bin()); feats[f].missing_type = m.missing_type();
       feats[f].bound_offset = static_cast<int>(bounds.size()); feats[f].bundle = bundle_of(f);
+      feats[f].num_categories = -1; feats[f].pad = 0;
+      if (m.is_categorical()) {   // the categories in ascending order, then their bins (bin 0's pseudo-category -1 is left out)
+        std::vector<std::pair<int, int>> cb;
+        for (int b = 1; b < m.num_bin(); ++b) cb.emplace_back(m.bin_2_categorical()[b], b);
+        std::sort(cb.begin(), cb.end());
+        feats[f].num_categories = static_cast<int>(cb.size());
+        for (auto& e : cb) bounds.push_back(static_cast<double>(e.first));
+        for (auto& e : cb) bounds.push_back(static_cast<double>(e.second));
+        continue;
+      }
       bounds.insert(bounds.end(), m.upper_bounds().begin(), m.upper_bounds().end());
     }
     int dev = device >= 0 ? device : 0;

@@ -65,7 +65,9 @@ GBDT::GBDT(const Dataset* train, const Config& config)
     const BinMapper& m = train_->mapper(f);
     meta[f].num_bin = m.num_bin(); meta[f].most_freq_bin = static_cast<int>(m.most_freq_bin());
     meta[f].default_bin = static_cast<int>(m.default_bin()); meta[f].missing_type = m.missing_type();
-    meta[f].real_index = train_->real_feature_index(f); meta[f].reserved = 0;
+    meta[f].real_index = train_->real_feature_index(f);
+    meta[f].bin_type = m.is_categorical() ? LGBCU_BIN_CATEGORICAL : LGBCU_BIN_NUMERICAL;
+    has_categorical_ = has_categorical_ || m.is_categorical();
     meta[f].penalty = config_.feature_contri.empty() ? 1.0 : config_.feature_contri[meta[f].real_index];
   }
   if (!config_.feature_contri.empty() && static_cast<int>(config_.feature_contri.size()) != train_->num_total_features())
@@ -85,6 +87,11 @@ GBDT::GBDT(const Dataset* train, const Config& config)
   tp.lambda_l2 = config_.lambda_l2; tp.min_gain_to_split = config_.min_gain_to_split;
   tp.max_delta_step = config_.max_delta_step; tp.path_smooth = config_.path_smooth;
   Check(lgbcu_set_tree_params(ctx_, &tp));
+  if (has_categorical_) {
+    if (data_parallel_) Log::Fatal("categorical features with tree_learner=data are outside this library's path");
+    Check(lgbcu_set_cat_params(ctx_, config_.cat_smooth, config_.cat_l2, config_.max_cat_threshold, config_.min_data_per_group,
+                               config_.max_cat_to_onehot));
+  }
   Check(lgbcu_set_hist_mode(ctx_, config_.hist_mode));
   st.tick("lgbcu_set_tree_params");
   const Metadata& md = train_->metadata();
@@ -325,9 +332,32 @@ bool GBDT::TrainOneIter(const float* grad, const float* hess) {
       Check(lgbcu_train_tree(ctx_, records_.data(), &ns));
       st.tick("lgbcu_train_tree");
       tree.reset(new Tree(config_.num_leaves));
+      std::vector<uint32_t> cat_sets;   // the tree's categorical bin sets (8 words each), if it has any
+      if (has_categorical_) {
+        int32_t nsets = 0;
+        Check(lgbcu_tree_cat_sets(ctx_, nullptr, 0, &nsets));
+        if (nsets > 0) { cat_sets.resize(static_cast<size_t>(nsets) * 8); Check(lgbcu_tree_cat_sets(ctx_, cat_sets.data(), nsets, &nsets)); }
+      }
       for (int i = 0; i < ns; ++i) {
         const LgbCuSplitRecord& r = records_[i];
         const BinMapper& m = train_->mapper(r.feature);
+        if (m.is_categorical()) {
+          // SerialTreeLearner::SplitInner, categorical branch (serial_tree_learner.cpp:592-621): the record names its set
+          // of bins; the model carries the set of the bins' category values
+          if (r.threshold < 0 || static_cast<size_t>(r.threshold) * 8 + 8 > cat_sets.size()) Log::Fatal("categorical split names bin set %d of %d", r.threshold, static_cast<int>(cat_sets.size() / 8));
+          const uint32_t* bin_set = cat_sets.data() + static_cast<size_t>(r.threshold) * 8;
+          std::vector<uint32_t> cat_set;   // Common::ConstructBitset over RealThreshold(bin)
+          for (int b = 0; b < m.num_bin(); ++b) {
+            if (!((bin_set[b >> 5] >> (b & 31)) & 1u)) continue;
+            const int v = static_cast<int>(m.BinToValue(b));
+            const int i1 = v / 32, i2 = v % 32;
+            if (static_cast<int>(cat_set.size()) < i1 + 1) cat_set.resize(i1 + 1, 0);
+            cat_set[i1] |= (1u << i2);
+          }
+          tree->SplitCategorical(r.leaf, r.feature, r.real_feature, bin_set, cat_set, r.left_output, r.right_output, r.left_count,
+                                 r.right_count, r.left_sum_hessian, r.right_sum_hessian, r.gain, m.missing_type());
+          continue;
+        }
         tree->Split(r.leaf, r.feature, r.real_feature, static_cast<uint32_t>(r.threshold), m.BinToValue(r.threshold),
                     r.left_output, r.right_output, r.left_count, r.right_count, r.left_sum_hessian, r.right_sum_hessian,
                     r.gain, m.missing_type(), r.default_left != 0);
@@ -353,6 +383,8 @@ bool GBDT::TrainOneIter(const float* grad, const float* hess) {
       tree->Shrinkage(shrinkage_rate_);
       // UpdateScore (gbdt.cpp:458-478): in-bag rows through the partition, out-of-bag rows by walking the tree
       Check(lgbcu_add_score_by_partition(ctx_, tree->leaf_values().data(), tree->num_leaves()));
+      if (tree->num_cat() > 0 && (bagged || !valid_.empty()))
+        Check(lgbcu_set_tree_cat_sets(ctx_, tree->cat_bin_sets().data(), tree->num_cat()));
       if (bagged) {
         std::vector<int> thr(tree->threshold_in_bin().begin(), tree->threshold_in_bin().end());
         Check(lgbcu_add_score_by_tree(ctx_, tree->num_leaves(), tree->split_feature_inner().data(), thr.data(),
@@ -440,6 +472,7 @@ void GBDT::AddValidData(const Dataset* valid) {
     const auto& t = models_[i];
     std::vector<int> thr(t->threshold_in_bin().begin(), t->threshold_in_bin().end());
     Check(lgbcu_set_class(ctx_, static_cast<int>(i % num_tree_per_iteration_)));
+    if (t->num_cat() > 0) Check(lgbcu_set_tree_cat_sets(ctx_, t->cat_bin_sets().data(), t->num_cat()));
     Check(lgbcu_valid_add_tree(ctx_, e.set, t->num_leaves(), t->split_feature_inner().data(), thr.data(),
                                t->decision_type().data(), t->left_child().data(), t->right_child().data(),
                                t->leaf_values().data()));
@@ -641,6 +674,7 @@ void GBDT::RollbackOneIter() {
     t.ScaleLeafValues(-1.0);   // Tree::Shrinkage(-1): subtracting the tree = adding its negative
     std::vector<int> thr(t.threshold_in_bin().begin(), t.threshold_in_bin().end());
     Check(lgbcu_set_class(ctx_, k));
+    if (t.num_cat() > 0) Check(lgbcu_set_tree_cat_sets(ctx_, t.cat_bin_sets().data(), t.num_cat()));
     Check(lgbcu_add_score_by_tree(ctx_, t.num_leaves(), t.split_feature_inner().data(), thr.data(), t.decision_type().data(),
                                   t.left_child().data(), t.right_child().data(), t.leaf_values().data(), nullptr, 0, 0));
     AddTreeToValid(t);

@@ -65,6 +65,7 @@ class GBDT {
   struct ValidEntry { const Dataset* data; int set; };
   void SetupNdcg(int set, const Metadata& md, int num_data);
   void AddTreeToValid(const Tree& tree);
+  bool has_categorical_ = false;   // some feature of the training data is categorical
   std::vector<MetricSpec> metrics_;
   std::vector<int> eval_at_;
   std::vector<ValidEntry> valid_;

@@ -58,6 +58,20 @@ int Tree::Split(int leaf, int feature_inner, int feature_real, uint32_t threshol
   return num_leaves_ - 1;
 }
 
+int Tree::SplitCategorical(int leaf, int feature_inner, int feature_real, const uint32_t* bin_set, const std::vector<uint32_t>& cat_set,
+                           double left_value, double right_value, int left_cnt, int right_cnt, double left_weight,
+                           double right_weight, float gain, int missing_type) {
+  const int node = num_leaves_ - 1;
+  const int right = Split(leaf, feature_inner, feature_real, static_cast<uint32_t>(num_cat_), static_cast<double>(num_cat_),
+                          left_value, right_value, left_cnt, right_cnt, left_weight, right_weight, gain, missing_type, false);
+  decision_type_[node] = static_cast<int8_t>(kCategoricalMask | (missing_type << 2));
+  ++num_cat_;
+  cat_boundaries_.push_back(cat_boundaries_.back() + static_cast<int>(cat_set.size()));
+  cat_threshold_.insert(cat_threshold_.end(), cat_set.begin(), cat_set.end());
+  cat_bin_sets_.insert(cat_bin_sets_.end(), bin_set, bin_set + 8);
+  return right;
+}
+
 void Tree::Shrinkage(double rate) {
   for (int i = 0; i < num_leaves_ - 1; ++i) {
     leaf_value_[i] = MaybeRoundToZero(leaf_value_[i] * rate);
@@ -81,7 +95,7 @@ std::string Tree::ToString() const {
   const size_t ni = static_cast<size_t>(num_leaves_ - 1), nl = static_cast<size_t>(num_leaves_);
   std::vector<int> dt(decision_type_.begin(), decision_type_.end());
   o << "num_leaves=" << num_leaves_ << '\n';
-  o << "num_cat=" << 0 << '\n';
+  o << "num_cat=" << num_cat_ << '\n';
   o << "split_feature=" << JoinInts(split_feature_, ni) << '\n';
   o << "split_gain=" << JoinG(split_gain_, ni) << '\n';
   o << "threshold=" << Join17(threshold_, ni) << '\n';
@@ -94,6 +108,13 @@ std::string Tree::ToString() const {
   o << "internal_value=" << JoinG(internal_value_, ni) << '\n';
   o << "internal_weight=" << JoinG(internal_weight_, ni) << '\n';
   o << "internal_count=" << JoinInts(internal_count_, ni) << '\n';
+  if (num_cat_ > 0) {
+    std::vector<int> ct(cat_threshold_.size());
+    o << "cat_boundaries=" << JoinInts(cat_boundaries_, static_cast<size_t>(num_cat_) + 1) << '\n';
+    o << "cat_threshold=";
+    for (size_t i = 0; i < cat_threshold_.size(); ++i) { if (i) o << ' '; o << cat_threshold_[i]; }
+    o << '\n';
+  }
   o << "shrinkage=" << shrinkage_ << '\n';
   o << '\n';
   return o.str();
@@ -116,9 +137,19 @@ Tree* Tree::FromString(const std::string& text) {
     return it->second;
   };
   const int nl = std::atoi(need("num_leaves").c_str());
-  if (kv.count("num_cat") && std::atoi(kv["num_cat"].c_str()) > 0) Log::Fatal("categorical splits are outside this library's path");
   std::unique_ptr<Tree> t(new Tree(std::max(nl, 2)));
   t->num_leaves_ = nl;
+  t->num_cat_ = kv.count("num_cat") ? std::atoi(kv["num_cat"].c_str()) : 0;
+  if (t->num_cat_ > 0) {   // src/io/tree.cpp:608-623
+    const std::string& b = need("cat_boundaries");
+    const std::string& c = need("cat_threshold");
+    t->cat_boundaries_.assign(static_cast<size_t>(t->num_cat_) + 1, 0);
+    const char* p = b.c_str(); char* end = nullptr;
+    for (int i = 0; i <= t->num_cat_; ++i) { t->cat_boundaries_[i] = static_cast<int>(std::strtol(p, &end, 10)); p = end; }
+    t->cat_threshold_.assign(static_cast<size_t>(t->cat_boundaries_.back()), 0u);
+    p = c.c_str();
+    for (size_t i = 0; i < t->cat_threshold_.size(); ++i) { t->cat_threshold_[i] = static_cast<uint32_t>(std::strtoul(p, &end, 10)); p = end; }
+  }
   auto doubles = [](const std::string& s, size_t n, std::vector<double>* out) {
     const char* p = s.c_str(); char* end = nullptr;
     for (size_t i = 0; i < n; ++i) { (*out)[i] = std::strtod(p, &end); p = end; }
@@ -156,6 +187,20 @@ double Tree::Predict(const double* x) const {
   while (node >= 0) {
     double fval = x[split_feature_[node]];
     const int missing_type = (decision_type_[node] >> 2) & 3;
+    if (decision_type_[node] & kCategoricalMask) {   // Tree::CategoricalDecision (tree.h:302-320)
+      // (static_cast<int> of a NaN or of a value outside the int range is undefined in the reference; on x86-64 it
+      // yields INT_MIN, i.e. "negative -> right", which is what is done here)
+      int iv = (fval > -2147483649.0 && fval < 2147483648.0) ? static_cast<int>(fval) : -1;
+      bool left = false;
+      if (iv >= 0) {
+        const int ci = static_cast<int>(threshold_[node]);
+        const int n = cat_boundaries_[ci + 1] - cat_boundaries_[ci];
+        const int i1 = iv / 32;
+        if (i1 < n) left = ((cat_threshold_[cat_boundaries_[ci] + i1] >> (iv % 32)) & 1u) != 0;
+      }
+      node = left ? left_child_[node] : right_child_[node];
+      continue;
+    }
     const bool default_left = (decision_type_[node] & kDefaultLeftMask) != 0;
     if (std::isnan(fval) && missing_type != kMissingNaN) fval = 0.0f;
     if ((missing_type == kMissingZero && (fval >= -kZeroThreshold && fval <= kZeroThreshold)) ||

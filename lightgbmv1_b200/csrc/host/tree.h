@@ -16,6 +16,13 @@ class Tree {
   int Split(int leaf, int feature_inner, int feature_real, uint32_t threshold_bin, double threshold_double,
             double left_value, double right_value, int left_cnt, int right_cnt, double left_weight,
             double right_weight, float gain, int missing_type, bool default_left);
+  // categorical split (Tree::SplitCategorical, src/io/tree.cpp:70-91): `bin_set` = 8 words, bit b = bin b goes left
+  // (the device's form of cat_threshold_inner_); `cat_set` = the bitset over the real category values (cat_threshold_)
+  int SplitCategorical(int leaf, int feature_inner, int feature_real, const uint32_t* bin_set, const std::vector<uint32_t>& cat_set,
+                       double left_value, double right_value, int left_cnt, int right_cnt, double left_weight,
+                       double right_weight, float gain, int missing_type);
+  int num_cat() const { return num_cat_; }
+  const std::vector<uint32_t>& cat_bin_sets() const { return cat_bin_sets_; }   // [num_cat][8]
   void Shrinkage(double rate);
   void AddBias(double val);
   void AsConstantTree(double val) { num_leaves_ = 1; shrinkage_ = 1.0f; leaf_value_[0] = val; }
@@ -39,6 +46,7 @@ class Tree {
   const std::vector<float>& split_gain() const { return split_gain_; }
   void ScaleLeafValues(double rate) { Shrinkage(rate); }
 
+  static const int8_t kCategoricalMask = 1;
   static const int8_t kDefaultLeftMask = 2;  // include/LightGBM/tree.h: kCategoricalMask = 1, kDefaultLeftMask = 2
 
  private:
@@ -55,6 +63,10 @@ class Tree {
   std::vector<int> internal_count_;
   std::vector<int> leaf_depth_;
   double shrinkage_;
+  int num_cat_ = 0;
+  std::vector<int> cat_boundaries_{0};
+  std::vector<uint32_t> cat_threshold_;
+  std::vector<uint32_t> cat_bin_sets_;
 };
 
 }  // namespace lgb

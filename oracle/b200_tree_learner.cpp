@@ -57,7 +57,7 @@ class CudaB200TreeLearner : public TreeLearner {
         Log::Fatal("CudaB200TreeLearner: feature %d needs more than 8-bit numerical bins", f);
       meta[f].num_bin = m->num_bin(); meta[f].most_freq_bin = static_cast<int>(m->GetMostFreqBin());
       meta[f].default_bin = static_cast<int>(m->GetDefaultBin()); meta[f].missing_type = static_cast<int>(m->missing_type());
-      meta[f].real_index = train_data->RealFeatureIndex(f); meta[f].reserved = 0; meta[f].penalty = 1.0;
+      meta[f].real_index = train_data->RealFeatureIndex(f); meta[f].bin_type = LGBCU_BIN_NUMERICAL; meta[f].penalty = 1.0;
     }
     Need(lgbcu_set_dataset_columns(ctx_, num_data_, F, ptrs.data(), meta.data()));
     PushParams();

@@ -190,8 +190,8 @@ def compare_models(text_a, text_b, rtol_value=1e-9, allow_near_ties=True, stop_a
     for i in range(n):
         a, b = ta[i], tb[i]
         ok = True
-        for k in ("num_leaves", "split_feature", "threshold", "decision_type", "left_child", "right_child",
-                  "leaf_count", "internal_count"):
+        for k in ("num_leaves", "num_cat", "split_feature", "threshold", "decision_type", "left_child", "right_child",
+                  "leaf_count", "internal_count", "cat_boundaries", "cat_threshold"):
             if a.get(k) != b.get(k):
                 ok = False
                 if first is None:

@@ -406,3 +406,46 @@ def test_bundled_features_bin_like_the_reference(shim, ref, ours, seed, n, param
         shim.ref_feature_bin_column(dvr, C.c_int(f), want.ctypes.data_as(C.POINTER(C.c_int32)))
         assert np.array_equal(bv[:, f], want), f"validation data, inner feature {f}: bins differ"
     ref.dataset_free(dr); ours.dataset_free(do); ours.dataset_free(do2)
+
+
+def categorical_matrix(seed, n, dtype=np.float64):
+    """columns 0, 2, 4, 5 are categorical: 3 categories (one-hot search), 60 skewed categories with NaN and negative
+    values, 400 categories of which many are rare, a sparse one (mostly category 0); 1, 3, 6 are numerical."""
+    rng = np.random.default_rng(seed)
+    c0 = rng.integers(0, 3, size=n).astype(np.float64)
+    c2 = np.floor(rng.exponential(8.0, size=n)).clip(0, 59)
+    c2 = np.where(rng.random(n) < 0.03, np.nan, c2)
+    c2 = np.where(rng.random(n) < 0.01, -2.0, c2)
+    c4 = np.floor(rng.pareto(1.2, size=n) * 3).clip(0, 399)
+    c5 = np.where(rng.random(n) < 0.9, 0.0, rng.integers(1, 12, size=n).astype(np.float64))
+    X = np.stack([c0, rng.standard_normal(n), c2, np.maximum(0, rng.standard_normal(n)), c4, c5,
+                  rng.standard_normal(n)], axis=1)
+    return X.astype(dtype)
+
+
+CAT_PARAMS = "categorical_feature=0,2,4,5 max_bin=255 verbosity=-1"
+
+
+@pytest.mark.parametrize("seed,n,extra", [(1, 20_000, ""), (2, 9_000, " max_bin=63 min_data_in_bin=5"), (3, 15_000, " use_missing=false")])
+def test_categorical_features_bin_like_the_reference(shim, ref, ours, seed, n, extra, monkeypatch):
+    monkeypatch.setenv("LGBM_B200_HOST_BINNING", "1")
+    X = categorical_matrix(seed, n)
+    p = CAT_PARAMS + extra
+    dr = ref.dataset_from_mat(X, p); do = ours.dataset_from_mat(X, p)
+    nf = shim.ref_num_inner_features(dr)
+    nfo = C.c_int(); ours.check(ours.lib.LGBM_B200_DatasetNumInnerFeatures(do, C.byref(nfo)))
+    assert nfo.value == nf
+    bins = np.empty((n, nf), dtype=np.int32); real = np.empty(nf, dtype=np.int32)
+    ours.check(ours.lib.LGBM_B200_DatasetDumpBins(do, bins.ctypes.data_as(C.POINTER(C.c_int32)), real.ctypes.data_as(C.POINTER(C.c_int32))))
+    for f in range(nf):
+        mr = (C.c_int32 * 5)(); br = (C.c_double * 600)()
+        mo = (C.c_int32 * 5)(); bo = (C.c_double * 600)()
+        shim.ref_feature_info(dr, C.c_int(f), mr, br, C.c_int(600))
+        ours.check(ours.lib.LGBM_B200_DatasetFeatureInfo(do, C.c_int(f), mo, bo, C.c_int(600)))
+        assert list(mr) == list(mo), f"inner feature {f}: (num_bin, mfb, default_bin, missing, real) differ"
+        # BinToValue: upper bounds of a numerical feature, the categories of a categorical one
+        assert np.array_equal(np.array(br[:mr[0]]), np.array(bo[:mo[0]]), equal_nan=True), f"inner feature {f}: BinToValue differs"
+        want = np.empty(n, dtype=np.int32)
+        shim.ref_feature_bin_column(dr, C.c_int(f), want.ctypes.data_as(C.POINTER(C.c_int32)))
+        assert np.array_equal(bins[:, f], want), f"inner feature {f} (column {real[f]}): bins differ"
+    ref.dataset_free(dr); ours.dataset_free(do)
