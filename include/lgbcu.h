@@ -349,6 +349,9 @@ LGBCU_API int lgbcu_valid_add_tree(LgbCuContext* ctx, int32_t set, int32_t num_l
  * threshold_bin = the index of its set among those staged with lgbcu_set_tree_cat_sets. */
 LGBCU_API int lgbcu_set_cat_params(LgbCuContext* ctx, double cat_smooth, double cat_l2, int32_t max_cat_threshold,
                                    int32_t min_data_per_group, int32_t max_cat_to_onehot);
+/* Monotone constraints, basic method (src/treelearner/monotone_constraints.hpp:19-126): one of -1 / 0 / +1 per inner
+ * feature (NULL: none) and Config::monotone_penalty.  Call after lgbcu_set_dataset. */
+LGBCU_API int lgbcu_set_monotone(LgbCuContext* ctx, const int8_t* types, int32_t num_features, double penalty);
 LGBCU_API int lgbcu_tree_cat_sets(LgbCuContext* ctx, uint32_t* out, int32_t cap_sets, int32_t* num_sets);
 LGBCU_API int lgbcu_set_tree_cat_sets(LgbCuContext* ctx, const uint32_t* sets, int32_t num_sets);
 LGBCU_API int lgbcu_valid_copy_score(LgbCuContext* ctx, int32_t set, double* out, int32_t n);

@@ -68,9 +68,11 @@ struct DevLeaf {     // DataPartition range + LeafSplits + pool slot of one leaf
   int gcount;        // rows of this leaf over ALL ranks (== count on one GPU); what the split search calls num_data
   double sum_g, sum_h;  // LeafSplits::sum_gradients/sum_hessians (from the parent's SplitInfo)
   double output;        // LeafSplits::weight (leaf output before shrinkage)
-  int pad0, pad1;
-  i64 reserved;
+  // monotone constraints, basic method (BasicLeafConstraints, monotone_constraints.hpp:88-126): the interval the
+  // leaf's output must stay in; inherited by the children, tightened by a split on a constrained feature
+  double mc_min, mc_max;
 };
+#define LGB_MC_INF 1.7976931348623157e308   /* std::numeric_limits<double>::max() */
 
 // Look-ahead growth.  The reference grows a tree best-first: split the open leaf with the largest gain, learn the
 // gains of its two children, repeat (serial_tree_learner.cpp:181-199).  Which leaves get split, and in which order, is
@@ -193,6 +195,9 @@ struct DevView {
   // categorical splits: an append-only pool of bin sets per tree.  A categorical candidate takes the next entry
   // (ctl->cat_count) and carries its index in DevSplit::threshold; partition, records and the host read the set there.
   int any_cat, cat_cap;
+  int use_mc;                     // Config::monotone_constraints is not empty (USE_MC of feature_histogram.hpp)
+  const signed char* monotone;    // [num_features] FeatureMetainfo::monotone_type
+  double mc_penalty;              // Config::monotone_penalty
   unsigned* cat_pool;        // [cat_cap][LGB_CAT_WORDS]
   DevCatParams cat;
 };

@@ -218,6 +218,8 @@ struct LgbCuContext {
   // categorical features: `general` = the data takes the general split search / partition instantiations (wide or
   // categorical feature present); the bin-set pool of the tree being grown; the sets staged for the tree walks
   bool any_cat = false, general = false; int cat_features = 0;
+  // monotone constraints (basic method): per-feature types on the device; every feature then takes the general search
+  bool use_mc = false; signed char* d_monotone = nullptr; double mc_penalty = 0.0;
   unsigned* d_cat_pool = nullptr; int cat_cap = 0;
   unsigned* d_tree_cat = nullptr; int tree_cat_count = 0, tree_cat_cap = 0;
   DevCatParams cat_params{10.0, 10.0, 32, 100, 4, 0};
@@ -303,6 +305,7 @@ struct LgbCuContext {
     V.num_data = N; V.num_features = F; V.row_stride = stride; V.total_bin = total_bin; V.num_tiles16 = ntiles16;
     V.num_storage = FS; V.any_wide = any_wide ? 1 : 0;
     V.any_cat = any_cat ? 1 : 0; V.cat_cap = cat_cap; V.cat_pool = d_cat_pool; V.cat = cat_params;
+    V.use_mc = use_mc ? 1 : 0; V.monotone = d_monotone; V.mc_penalty = mc_penalty;
     V.bins = d_bins; V.feats = d_feats; V.feat_used = d_feat_used; V.splittable = d_splittable;
     V.parent_split = d_parent_split; V.mfb_fix = d_mfb_fix; V.spec = d_spec; V.expanded = d_expanded; V.pool_slots = pool_slots;
     V.bits_stride = bits_stride; V.part_sync_stride = part_sync_stride;
@@ -722,6 +725,7 @@ int lgbcu_destroy(LgbCuContext* c) {
   lgbcu_comm_destroy(c);
   free_valid_sets(c);
   if (c->d_cat_pool) { lgb_dev_free(c->d_cat_pool); c->d_cat_pool = nullptr; }
+  if (c->d_monotone) { lgb_dev_free(c->d_monotone); c->d_monotone = nullptr; }
   if (c->d_tree_cat) { lgb_dev_free(c->d_tree_cat); c->d_tree_cat = nullptr; }
   void* ptrs[] = {c->d_bins, c->d_feats, c->d_feat_used, c->d_grad_base, c->d_hess_base, c->d_gh, c->d_label, c->d_weight, c->d_score_base,
                   c->d_indices[0], c->d_indices[1], c->d_part_bits, c->d_part_sync, c->d_bins_col, c->d_query, c->d_label_gain,
@@ -776,6 +780,7 @@ static int setup_dataset_common(LgbCuContext* c, int32_t num_data, int32_t num_f
     base += d.nslots;
   }
   {
+    c->use_mc = false;   // lgbcu_set_monotone follows the dataset
     c->general = c->any_wide || c->any_cat;
     const int fb = c->general ? KEY_FEAT_BITS_WIDE : KEY_FEAT_BITS;
     NEED(num_features < (1 << fb), "lgbcu_set_dataset: %d features exceed the supported %d%s", num_features, (1 << fb) - 1,
@@ -1146,6 +1151,28 @@ int lgbcu_set_cat_params(LgbCuContext* c, double cat_smooth, double cat_l2, int3
        "lgbcu_set_cat_params: parameter out of range");
   c->cat_params = DevCatParams{cat_smooth, cat_l2, max_cat_threshold, min_data_per_group, max_cat_to_onehot, 0};
   drop_graph(c);   // the captured launches hold the parameters by value
+  return 0;
+}
+
+// Monotone constraints, basic method (Config::monotone_constraints per inner feature: -1 / 0 / +1, and monotone_penalty;
+// LeafConstraintsBase / BasicLeafConstraints, src/treelearner/monotone_constraints.hpp).  types = NULL: none.
+int lgbcu_set_monotone(LgbCuContext* c, const int8_t* types, int32_t num_features, double penalty) {
+  NEED(c && c->F > 0, "lgbcu_set_monotone: dataset not set");
+  USE_DEVICE(c->device);
+  drop_graph(c);   // the captured launches hold the view by value
+  if (!types) { c->use_mc = false; c->general = c->any_wide || c->any_cat; return 0; }
+  NEED(num_features == c->F, "lgbcu_set_monotone: %d types for %d features", num_features, c->F);
+  NEED(penalty >= 0.0, "lgbcu_set_monotone: monotone_penalty should be >= 0");
+  NEED(!c->comm, "lgbcu_set_monotone: monotone constraints with tree_learner=data are outside this library's path");
+  for (int f = 0; f < num_features; ++f) {
+    NEED(types[f] >= -1 && types[f] <= 1, "lgbcu_set_monotone: type of feature %d is %d", f, (int)types[f]);
+    NEED(types[f] == 0 || !c->h_feats[f].cat, "The output cannot be monotone with respect to categorical features");
+  }
+  NEED(c->F < (1 << KEY_FEAT_BITS_WIDE), "lgbcu_set_monotone: %d features exceed the supported %d for constrained data", c->F, (1 << KEY_FEAT_BITS_WIDE) - 1);
+  CU(dev_alloc(&c->d_monotone, (size_t)num_features));
+  CU(cudaMemcpyAsync(c->d_monotone, types, (size_t)num_features, cudaMemcpyHostToDevice, c->stream));
+  CU(cudaStreamSynchronize(c->stream));
+  c->use_mc = true; c->mc_penalty = penalty; c->general = true;
   return 0;
 }
 

@@ -193,7 +193,7 @@ __global__ void k_prepare_tree(DevView V, int root_count, int root_identity, int
     V.best[l] = none;
     { SplitKey k; k.gain = LGB_MIN_SCORE; k.real_feature = -1; k.pad = 0; V.leaf_key[l] = k; }
     DevLeaf z; z.begin = 0; z.count = 0; z.slot = l; z.depth = 0; z.buf = 0; z.gcount = 0;
-    z.sum_g = z.sum_h = z.output = 0; z.pad0 = z.pad1 = 0; z.reserved = 0;
+    z.sum_g = z.sum_h = z.output = 0; z.mc_min = -LGB_MC_INF; z.mc_max = LGB_MC_INF;
     if (l == 0) { z.count = root_count; z.gcount = groot; }
     V.leaves[l] = z;
     V.expanded[l] = 0;

@@ -96,6 +96,16 @@ __device__ void part_expand(const DevView& V, int e, int leaf, const DevLeaf& L,
   A.gcount = gl; B.gcount = gr;
   A.sum_g = s.left_sum_g; A.sum_h = s.left_sum_h; A.output = s.left_output;
   B.sum_g = s.right_sum_g; B.sum_h = s.right_sum_h; B.output = s.right_output;
+  if (V.use_mc) {
+    // BasicLeafConstraints::Update (monotone_constraints.hpp:100-117): both children start from the leaf's interval (A
+    // and B are copies of L); a numerical split on a constrained feature puts the mean of the two outputs between them
+    const int type = V.monotone[s.feature];
+    if (type != 0 && !V.feats[s.feature].cat) {
+      const double mid = (s.left_output + s.right_output) / 2.0f;
+      if (type < 0) { A.mc_min = fmax(mid, A.mc_min); B.mc_max = fmin(mid, B.mc_max); }
+      else { A.mc_max = fmin(mid, A.mc_max); B.mc_min = fmax(mid, B.mc_min); }
+    }
+  }
   // the larger child inherits the parent's slot (subtraction happens in place); the smaller one gets a fresh slot
   // whose index depends on (round, item) only, so the host can address it blind (data-parallel all-reduce)
   const int fresh = 1 + (c->round - 1) * c->lookahead + e;

@@ -607,7 +607,7 @@ __device__ void find_item(const DevView& V, ScanSmem& S, int f, int sel, const F
     // them.  The data-parallel learner overrides FindBestSplits without that mask (data_parallel_tree_learner.cpp:
     // 155-173: every by-tree feature is histogrammed and scanned for every leaf), so there the flags are not applied.
     if (T.has_larger && T.parent_split && !V.data_parallel) used = used && T.parent_split[f] != 0;
-    if (WIDE && (F.wide || F.cat)) { find_item_wide(V, S, f, sel, T, F, used != 0); return; }   // more than 256 stored values, or categorical: the general search
+    if (WIDE && (F.wide || F.cat || V.use_mc)) { find_item_wide(V, S, f, sel, T, F, used != 0); return; }   // more than 256 stored values, or categorical: the general search
     const int nt = F.num_bin - F.offset;
     const double inv_g = c->inv_g, inv_h = c->inv_h;
     HistEntry* hs = V.pool + (size_t)Ls.slot * V.total_bin + F.hist_base;  // smaller leaf, slot 0 of the group

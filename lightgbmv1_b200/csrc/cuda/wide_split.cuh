@@ -17,6 +17,29 @@ struct WideData {   // data_[t] of FeatureHistogram for one (feature, leaf): ent
   __device__ __forceinline__ double hh(int t) const { return t == mfb ? fix_h : (double)h[1 + t].h * inv_h; }
 };
 
+
+// Monotone constraints (USE_MC of feature_histogram.hpp:763-824).  `MC` = {use, min, max, type}: with use = 0 these are
+// the plain forms.
+struct McInfo { int use; double lo, hi; int type; };
+__device__ __forceinline__ double mc_output(double g, double h, const DevParams& P, int n, double parent_output, const McInfo& M) {
+  double ret = leaf_output(g, h, P, n, parent_output);
+  if (M.use) { if (ret < M.lo) ret = M.lo; else if (ret > M.hi) ret = M.hi; }   // CalculateSplittedLeafOutput<USE_MC>
+  return ret;
+}
+__device__ __forceinline__ double gain_given_output(double g, double h, const DevParams& P, double out) {   // GetLeafGainGivenOutput
+  const double sg = P.use_l1 ? threshold_l1(g, P.lambda_l1) : g;
+  return -(2.0 * sg * out + (h + P.lambda_l2) * out * out);
+}
+// GetSplitGains (feature_histogram.hpp:781-824)
+__device__ __forceinline__ double mc_split_gains(double lg, double lh, double rg, double rh, const DevParams& P, int lc, int rc,
+                                                 double parent_output, const McInfo& M) {
+  if (!M.use) return leaf_gain(lg, lh, P, lc, parent_output) + leaf_gain(rg, rh, P, rc, parent_output);
+  const double lo = mc_output(lg, lh, P, lc, parent_output, M);
+  const double ro = mc_output(rg, rh, P, rc, parent_output, M);
+  if ((M.type > 0 && lo > ro) || (M.type < 0 && lo < ro)) return 0;
+  return gain_given_output(lg, lh, P, lo) + gain_given_output(rg, rh, P, ro);
+}
+
 struct WideBest { double gain, left_g, left_h; int left_count, threshold; bool found; };
 
 // One direction of FindBestThresholdSequentially.  Returns the best candidate of the direction (found = false: none
@@ -24,7 +47,7 @@ struct WideBest { double gain, left_g, left_h; int left_count, threshold; bool f
 template <bool REVERSE>
 __device__ WideBest wide_scan(const WideData& D, const DevFeat& F, const DevParams& P, bool skip_default, bool na_missing,
                               double sum_g, double sum_h, int num_data, double min_gain_shift, double parent_output,
-                              int* splittable) {
+                              const McInfo& M, int* splittable) {
   const int offset = F.offset;
   WideBest B; B.gain = LGB_MIN_SCORE; B.left_g = 0; B.left_h = 0; B.left_count = 0; B.threshold = F.num_bin; B.found = false;
   const double cnt_factor = num_data / sum_h;
@@ -42,7 +65,7 @@ __device__ WideBest wide_scan(const WideData& D, const DevFeat& F, const DevPara
       const double lh = sum_h - rh;
       if (lh < P.min_sum_hessian) break;
       const double lg = sum_g - rg;
-      const double gain = leaf_gain(lg, lh, P, lc, parent_output) + leaf_gain(rg, rh, P, rc, parent_output);
+      const double gain = mc_split_gains(lg, lh, rg, rh, P, lc, rc, parent_output, M);
       if (gain <= min_gain_shift) continue;
       *splittable = 1;
       if (gain > B.gain) { B.left_count = lc; B.left_g = lg; B.left_h = lh; B.threshold = t - 1 + offset; B.gain = gain; B.found = true; }
@@ -71,7 +94,7 @@ __device__ WideBest wide_scan(const WideData& D, const DevFeat& F, const DevPara
       const double rh = sum_h - lh;
       if (rh < P.min_sum_hessian) break;
       const double rg = sum_g - lg;
-      const double gain = leaf_gain(lg, lh, P, lc, parent_output) + leaf_gain(rg, rh, P, rc, parent_output);
+      const double gain = mc_split_gains(lg, lh, rg, rh, P, lc, rc, parent_output, M);
       if (gain <= min_gain_shift) continue;
       *splittable = 1;
       if (gain > B.gain) { B.left_count = lc; B.left_g = lg; B.left_h = lh; B.threshold = t + offset; B.gain = gain; B.found = true; }
@@ -82,7 +105,7 @@ __device__ WideBest wide_scan(const WideData& D, const DevFeat& F, const DevPara
 
 // FindBestThreshold (feature_histogram.hpp:85-95, FuncForNumricalL3 :156-217) of one (feature, leaf) by ONE thread
 __device__ void wide_find_best_threshold(const WideData& D, const DevFeat& F, const DevParams& P, double sum_g, double leaf_sum_h,
-                                         int num_data, double parent_output, DevSplit* out, int* splittable_out) {
+                                         int num_data, double parent_output, const McInfo& M, DevSplit* out, int* splittable_out) {
   DevSplit o;
   o.gain = LGB_MIN_SCORE; o.feature = -1; o.real_feature = -1; o.threshold = 0; o.default_left = 1;
   o.left_count = 0; o.right_count = 0; o.left_output = 0; o.right_output = 0;
@@ -93,11 +116,11 @@ __device__ void wide_find_best_threshold(const WideData& D, const DevFeat& F, co
   auto apply = [&](const WideBest& B, int default_left) {   // the tail of FindBestThresholdSequentially
     if (!(splittable && B.found && B.gain > o.gain + min_gain_shift)) return;
     o.threshold = B.threshold;
-    o.left_output = leaf_output(B.left_g, B.left_h, P, B.left_count, parent_output);
+    o.left_output = mc_output(B.left_g, B.left_h, P, B.left_count, parent_output, M);
     o.left_count = B.left_count;
     o.left_sum_g = B.left_g;
     o.left_sum_h = B.left_h - LGB_EPS;
-    o.right_output = leaf_output(sum_g - B.left_g, sum_h - B.left_h, P, num_data - B.left_count, parent_output);
+    o.right_output = mc_output(sum_g - B.left_g, sum_h - B.left_h, P, num_data - B.left_count, parent_output, M);
     o.right_count = num_data - B.left_count;
     o.right_sum_g = sum_g - B.left_g;
     o.right_sum_h = sum_h - B.left_h - LGB_EPS;
@@ -106,10 +129,10 @@ __device__ void wide_find_best_threshold(const WideData& D, const DevFeat& F, co
   };
   if (F.num_bin > 2 && F.missing_type != LGBCU_MISSING_NONE) {
     const bool zero = F.missing_type == LGBCU_MISSING_ZERO;
-    apply(wide_scan<true>(D, F, P, zero, !zero, sum_g, sum_h, num_data, min_gain_shift, parent_output, &splittable), 1);
-    apply(wide_scan<false>(D, F, P, zero, !zero, sum_g, sum_h, num_data, min_gain_shift, parent_output, &splittable), 0);
+    apply(wide_scan<true>(D, F, P, zero, !zero, sum_g, sum_h, num_data, min_gain_shift, parent_output, M, &splittable), 1);
+    apply(wide_scan<false>(D, F, P, zero, !zero, sum_g, sum_h, num_data, min_gain_shift, parent_output, M, &splittable), 0);
   } else {
-    apply(wide_scan<true>(D, F, P, false, false, sum_g, sum_h, num_data, min_gain_shift, parent_output, &splittable), 1);
+    apply(wide_scan<true>(D, F, P, false, false, sum_g, sum_h, num_data, min_gain_shift, parent_output, M, &splittable), 1);
     if (F.missing_type == LGBCU_MISSING_NAN) o.default_left = 0;
   }
   o.gain *= F.penalty;
@@ -125,7 +148,7 @@ __device__ void wide_find_best_threshold(const WideData& D, const DevFeat& F, co
 // are accumulated from the low end and from the high end, up to max_cat_threshold bins a side.  `sorted` = scratch in
 // shared memory for 256 bin indices; `bits` = LGB_CAT_WORDS words that receive the set of BINS going left.
 __device__ void cat_find_best_threshold(const WideData& D, const DevFeat& F, const DevParams& P0, const DevCatParams& C,
-                                        double sum_g, double leaf_sum_h, int num_data, double parent_output,
+                                        double sum_g, double leaf_sum_h, int num_data, double parent_output, const McInfo& M,
                                         unsigned char* sorted, double* ctr, unsigned* bits, DevSplit* out, int* splittable_out) {
   DevSplit o;
   o.gain = LGB_MIN_SCORE; o.feature = -1; o.real_feature = -1; o.threshold = 0; o.default_left = 0;
@@ -160,8 +183,7 @@ __device__ void cat_find_best_threshold(const WideData& D, const DevFeat& F, con
       const double sum_other_h = sum_h - hess - LGB_EPS;
       if (sum_other_h < P.min_sum_hessian) continue;
       const double sum_other_g = sum_g - grad;
-      const double gain = leaf_gain(sum_other_g, sum_other_h, P, other_count, parent_output) +
-                          leaf_gain(grad, hess + LGB_EPS, P, cnt, parent_output);
+      const double gain = mc_split_gains(sum_other_g, sum_other_h, grad, hess + LGB_EPS, P, other_count, cnt, parent_output, M);
       if (gain <= min_gain_shift) continue;
       splittable = 1;
       if (gain > best_gain) { best_threshold = t; best_lg = grad; best_lh = hess + LGB_EPS; best_lc = cnt; best_gain = gain; }
@@ -203,7 +225,7 @@ __device__ void cat_find_best_threshold(const WideData& D, const DevFeat& F, con
         if (cnt_cur_group < C.min_data_per_group) continue;
         cnt_cur_group = 0;
         const double rg = sum_g - lg;
-        const double gain = leaf_gain(lg, lh, P, left_count, parent_output) + leaf_gain(rg, rh, P, right_count, parent_output);
+        const double gain = mc_split_gains(lg, lh, rg, rh, P, left_count, right_count, parent_output, M);
         if (gain <= min_gain_shift) continue;
         splittable = 1;
         if (gain > best_gain) { best_lc = left_count; best_lg = lg; best_lh = lh; best_threshold = i; best_gain = gain; best_dir = dir; }
@@ -212,11 +234,11 @@ __device__ void cat_find_best_threshold(const WideData& D, const DevFeat& F, con
   }
   for (int w = 0; w < LGB_CAT_WORDS; ++w) bits[w] = 0u;
   if (splittable) {
-    o.left_output = leaf_output(best_lg, best_lh, P, best_lc, parent_output);
+    o.left_output = mc_output(best_lg, best_lh, P, best_lc, parent_output, M);
     o.left_count = best_lc;
     o.left_sum_g = best_lg;
     o.left_sum_h = best_lh - LGB_EPS;
-    o.right_output = leaf_output(sum_g - best_lg, sum_h - best_lh, P, num_data - best_lc, parent_output);
+    o.right_output = mc_output(sum_g - best_lg, sum_h - best_lh, P, num_data - best_lc, parent_output, M);
     o.right_count = num_data - best_lc;
     o.right_sum_g = sum_g - best_lg;
     o.right_sum_h = sum_h - best_lh - LGB_EPS;
@@ -301,10 +323,15 @@ __device__ void find_item_wide(const DevView& V, ScanSmem& S, int f, int sel, co
     if (tid == 0) {
       WideData D; D.h = ht; D.mfb = F.mfb > 0 ? F.mfb : -1000; D.fix_g = s_fix[0]; D.fix_h = s_fix[1]; D.inv_g = inv_g; D.inv_h = inv_h;
       const bool id0 = sel == 0 ? T.smaller_id0 : T.larger_id0;
-      const double parent_output = parent_output_of(Lt, id0 ? 0 : 1, V.p);
+      double parent_output = parent_output_of(Lt, id0 ? 0 : 1, V.p);
+      // the leaf with id 0 takes its own unsmoothed output as "parent" output -- clamped to its interval
+      // (CalculateSplittedLeafOutput<true, ...> with constraints_->Get(0), serial_tree_learner.cpp:709-715)
+      if (id0 && V.use_mc) parent_output = fmin(fmax(parent_output, Lt.mc_min), Lt.mc_max);
+      McInfo M; M.use = V.use_mc; M.lo = Lt.mc_min; M.hi = Lt.mc_max; M.type = 0;
+      if (V.use_mc && !F.cat) M.type = V.monotone[f];
       if (F.cat) {
         unsigned bits[LGB_CAT_WORDS];
-        cat_find_best_threshold(D, F, V.p, V.cat, Lt.sum_g, Lt.sum_h, Lt.gcount, parent_output, s_sorted, s_ctr, bits, &o, &sp);
+        cat_find_best_threshold(D, F, V.p, V.cat, Lt.sum_g, Lt.sum_h, Lt.gcount, parent_output, M, s_sorted, s_ctr, bits, &o, &sp);
         if (sp) {   // the set of bins going left takes the next pool entry; the split carries its index as "threshold"
           const int e = atomicAdd(&c->cat_count, 1);
           if (e < V.cat_cap) {
@@ -315,7 +342,17 @@ __device__ void find_item_wide(const DevView& V, ScanSmem& S, int f, int sel, co
           }
         }
       } else {
-        wide_find_best_threshold(D, F, V.p, Lt.sum_g, Lt.sum_h, Lt.gcount, parent_output, &o, &sp);
+        wide_find_best_threshold(D, F, V.p, Lt.sum_g, Lt.sum_h, Lt.gcount, parent_output, M, &o, &sp);
+        if (M.type != 0) {
+          // SerialTreeLearner::ComputeBestSplitForFeature (serial_tree_learner.cpp:728-732) with
+          // LeafConstraintsBase::ComputeMonotoneSplitGainPenalty (monotone_constraints.hpp:66-75)
+          const double pen = V.mc_penalty; const int depth = Lt.depth;
+          double factor;
+          if (pen >= depth + 1.) factor = LGB_EPS;
+          else if (pen <= 1.) factor = 1. - pen / pow(2., (double)depth) + LGB_EPS;
+          else factor = 1. - pow(2., pen - 1. - depth) + LGB_EPS;
+          o.gain *= factor;
+        }
       }
       o.feature = f; o.real_feature = F.real_index;
     }

@@ -42,6 +42,9 @@ const std::unordered_map<std::string, std::string>& Aliases() {
       {"map_eval_at", "eval_at"}, {"map_at", "eval_at"}, {"num_machine", "num_machines"},
       {"feature_contrib", "feature_contri"}, {"fc", "feature_contri"}, {"fp", "feature_contri"}, {"feature_penalty", "feature_contri"},
       {"num_classes", "num_class"},
+      {"mc", "monotone_constraints"}, {"monotone_constraint", "monotone_constraints"},
+      {"monotone_constraining_method", "monotone_constraints_method"}, {"mc_method", "monotone_constraints_method"},
+      {"monotone_splits_penalty", "monotone_penalty"}, {"ms_penalty", "monotone_penalty"}, {"mc_penalty", "monotone_penalty"},
       {"cat_feature", "categorical_feature"}, {"categorical_column", "categorical_feature"}, {"cat_column", "categorical_feature"},
   };
   return t;
@@ -317,7 +320,18 @@ void Config::Set(const std::unordered_map<std::string, std::string>& p) {
   if (feature_fraction_bynode < 1.0) Log::Fatal("feature_fraction_bynode < 1 is outside this library's path");
   if (pos_bagging_fraction <= 0.0 || pos_bagging_fraction > 1.0) Log::Fatal("pos_bagging_fraction should be in (0, 1]");
   if (neg_bagging_fraction <= 0.0 || neg_bagging_fraction > 1.0) Log::Fatal("neg_bagging_fraction should be in (0, 1]");
-  for (const char* k : {"monotone_constraints", "forcedsplits_filename", "forcedbins_filename", "interaction_constraints",
+  if (GetStr(p, "monotone_constraints", &s) && !s.empty()) {
+    monotone_constraints.clear();
+    for (auto& t : SplitAny(s, ",")) monotone_constraints.push_back(static_cast<int8_t>(std::atoi(t.c_str())));
+    for (int8_t v : monotone_constraints) if (v < -1 || v > 1) Log::Fatal("monotone_constraints should be -1, 0 or 1");
+    // (an all-zero list still selects the constrained code path in the reference -- USE_MC = !empty(), feature_histogram.hpp:
+    // 117 -- whose gains are formed from the outputs; kept as given)
+  }
+  if (GetStr(p, "monotone_constraints_method", &s) && s != "basic")
+    Log::Fatal("monotone_constraints_method=%s is outside this library's path (basic is built)", s.c_str());
+  GetDouble(p, "monotone_penalty", &monotone_penalty);
+  if (monotone_penalty < 0.0) Log::Fatal("monotone_penalty should be >= 0");
+  for (const char* k : {"forcedsplits_filename", "forcedbins_filename", "interaction_constraints",
                         "cegb_penalty_feature_lazy", "cegb_penalty_feature_coupled", "max_bin_by_feature",
                         "linear_tree"}) {
     if (GetStr(p, k, &s)) Log::Fatal("parameter %s is outside this library's path", k);

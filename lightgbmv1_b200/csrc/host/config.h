@@ -61,6 +61,9 @@ struct Config {
   std::vector<int> categorical_feature;
   int min_data_per_group = 100, max_cat_threshold = 32, max_cat_to_onehot = 4;
   double cat_l2 = 10.0, cat_smooth = 10.0;
+  // monotone constraints (basic method): -1 / 0 / +1 per raw column; monotone_penalty
+  std::vector<int8_t> monotone_constraints;
+  double monotone_penalty = 0.0;
   bool is_unbalance = false;
   double scale_pos_weight = 1.0;
   bool boost_from_average = true;

@@ -92,6 +92,17 @@ GBDT::GBDT(const Dataset* train, const Config& config)
     Check(lgbcu_set_cat_params(ctx_, config_.cat_smooth, config_.cat_l2, config_.max_cat_threshold, config_.min_data_per_group,
                                config_.max_cat_to_onehot));
   }
+  if (!config_.monotone_constraints.empty()) {
+    if (static_cast<int>(config_.monotone_constraints.size()) != train_->num_total_features())
+      Log::Fatal("Check failed: (num_total_features_) == (io_config.monotone_constraints.size())");
+    if (data_parallel_) Log::Fatal("monotone constraints with tree_learner=data are outside this library's path");
+    std::vector<int8_t> types(F);
+    for (int f = 0; f < F; ++f) {
+      types[f] = config_.monotone_constraints[train_->real_feature_index(f)];
+      if (types[f] != 0 && train_->mapper(f).is_categorical()) Log::Fatal("The output cannot be monotone with respect to categorical features");
+    }
+    Check(lgbcu_set_monotone(ctx_, types.data(), F, config_.monotone_penalty));
+  }
   Check(lgbcu_set_hist_mode(ctx_, config_.hist_mode));
   st.tick("lgbcu_set_tree_params");
   const Metadata& md = train_->metadata();
