@@ -40,6 +40,19 @@ LGBM_B200_API int LGBM_RegisterLogCallback(void (*callback)(const char*));
 /* c_api.h:229-236  (src/c_api.cpp:998-1015 -> :1018-1100) */
 LGBM_B200_API int LGBM_DatasetCreateFromMat(const void* data, int data_type, int32_t nrow, int32_t ncol, int is_row_major,
                                             const char* parameters, const DatasetHandle reference, DatasetHandle* out);
+/* c_api.h:160-170, 205-215  (src/c_api.cpp:1102-1171, 1239-1318): sparse input.  The matrix is densified on the host (absent
+ * entries = 0.0) and takes the LGBM_DatasetCreateFromMat path: the same bin mappers, bundles and bins. */
+LGBM_B200_API int LGBM_DatasetCreateFromCSR(const void* indptr, int indptr_type, const int32_t* indices, const void* data,
+                                            int data_type, int64_t nindptr, int64_t nelem, int64_t num_col, const char* parameters,
+                                            const DatasetHandle reference, DatasetHandle* out);
+LGBM_B200_API int LGBM_DatasetCreateFromCSC(const void* col_ptr, int col_ptr_type, const int32_t* indices, const void* data,
+                                            int data_type, int64_t ncol_ptr, int64_t nelem, int64_t num_row, const char* parameters,
+                                            const DatasetHandle reference, DatasetHandle* out);
+/* c_api.h:750-764  (src/c_api.cpp:1893-1943) */
+LGBM_B200_API int LGBM_BoosterPredictForCSR(BoosterHandle handle, const void* indptr, int indptr_type, const int32_t* indices,
+                                            const void* data, int data_type, int64_t nindptr, int64_t nelem, int64_t num_col,
+                                            int predict_type, int start_iteration, int num_iteration, const char* parameter,
+                                            int64_t* out_len, double* out_result);
 /* c_api.h:344-348  (src/c_api.cpp:1422-1439) field_name: label | weight | group/query | init_score */
 LGBM_B200_API int LGBM_DatasetSetField(DatasetHandle handle, const char* field_name, const void* field_data,
                                        int num_element, int type);

@@ -114,6 +114,77 @@ LoadedModel* ParseModel(const std::string& text) {
   catch (...) { SetLastError("unknown exception"); return -1; }         \
   return 0;
 
+namespace {
+
+// Sparse input (LGBM_DatasetCreateFromCSR / CSC, src/c_api.cpp:1102-1171, 1239-1318) -> the dense row-major matrix the
+// device path consumes: absent entries are 0.0.  The reference samples and pushes the same values either way (its
+// per-column sample lists hold the non-zero sampled values in sample order for a dense, a CSR and a CSC source alike),
+// so the dataset is the one LGBM_DatasetCreateFromMat builds from the densified matrix.  (One corner differs: in a CSR
+// row the reference pushes the implied zeros of features whose zero bin is not their most frequent bin AFTER the
+// stored entries, Dataset::FinishOneRow, which changes who wins a bundle conflict in such a row.)
+int64_t IndptrAt(const void* p, int type, int64_t i) {
+  return type == C_API_DTYPE_INT32 ? static_cast<int64_t>(static_cast<const int32_t*>(p)[i]) : static_cast<const int64_t*>(p)[i];
+}
+
+template <typename T>
+void Densify(bool csr, const void* ptr, int ptr_type, const int32_t* indices, const void* data, int data_type, int64_t nptr,
+             int64_t nrow, int64_t ncol, int64_t row0, int64_t rows, T* out) {
+  std::fill(out, out + static_cast<size_t>(rows) * ncol, T(0));
+  int bad = 0;
+  auto value = [&](int64_t k) -> T {
+    return data_type == C_API_DTYPE_FLOAT32 ? static_cast<T>(static_cast<const float*>(data)[k]) : static_cast<T>(static_cast<const double*>(data)[k]);
+  };
+  if (csr) {
+#pragma omp parallel for schedule(static)
+    for (int64_t r = 0; r < rows; ++r) {
+      const int64_t b = IndptrAt(ptr, ptr_type, row0 + r), e = IndptrAt(ptr, ptr_type, row0 + r + 1);
+      for (int64_t k = b; k < e; ++k) {
+        const int32_t c = indices[k];
+        if (c < 0 || c >= ncol) { bad = 1; continue; }   // (no exception may leave a parallel region)
+        out[static_cast<size_t>(r) * ncol + c] = value(k);
+      }
+    }
+  } else {
+#pragma omp parallel for schedule(static)
+    for (int64_t c = 0; c < nptr - 1; ++c) {
+      const int64_t b = IndptrAt(ptr, ptr_type, c), e = IndptrAt(ptr, ptr_type, c + 1);
+      for (int64_t k = b; k < e; ++k) {
+        const int64_t r = indices[k];
+        if (r < 0 || r >= nrow) { bad = 1; continue; }
+        if (r >= row0 && r < row0 + rows) out[static_cast<size_t>(r - row0) * ncol + c] = value(k);
+      }
+    }
+  }
+  if (bad) Log::Fatal(csr ? "Check failed: (inner_data.first) < (num_col)" : "row index out of range in CSC input");
+}
+
+Dataset* DatasetFromSparse(bool csr, const void* ptr, int ptr_type, const int32_t* indices, const void* data, int data_type,
+                           int64_t nptr, int64_t nrow, int64_t ncol, const char* parameters, const DatasetHandle reference) {
+  if (!ptr || !indices || !data) Log::Fatal("LGBM_DatasetCreateFromCS%c: NULL argument", csr ? 'R' : 'C');
+  if (ptr_type != C_API_DTYPE_INT32 && ptr_type != C_API_DTYPE_INT64) Log::Fatal("Unknown data type in RowFunctionFromCSR");
+  if (data_type != C_API_DTYPE_FLOAT32 && data_type != C_API_DTYPE_FLOAT64) Log::Fatal("Unknown data type in RowFunctionFromCSR");
+  if (ncol <= 0) Log::Fatal("The number of columns should be greater than zero.");
+  if (ncol >= INT32_MAX) Log::Fatal("The number of columns should be smaller than INT32_MAX.");
+  if (nrow <= 0 || nrow >= INT32_MAX) Log::Fatal("Check failed: (num_data) > (0)");
+  const size_t cells = static_cast<size_t>(nrow) * static_cast<size_t>(ncol);
+  const size_t esz = data_type == C_API_DTYPE_FLOAT32 ? 4 : 8;
+  if (cells * esz > (static_cast<size_t>(96) << 30))
+    Log::Fatal("sparse input of %lld x %lld would need %.1f GB as the dense matrix this library trains on", static_cast<long long>(nrow),
+               static_cast<long long>(ncol), static_cast<double>(cells * esz) / 1073741824.0);
+  Config config;
+  config.Set(Config::Str2Map(parameters));
+  if (config.num_threads > 0) omp_set_num_threads(config.num_threads);
+  std::unique_ptr<char[]> dense(new char[cells * esz]);
+  if (esz == 4) Densify<float>(csr, ptr, ptr_type, indices, data, data_type, nptr, nrow, ncol, 0, nrow, reinterpret_cast<float*>(dense.get()));
+  else Densify<double>(csr, ptr, ptr_type, indices, data, data_type, nptr, nrow, ncol, 0, nrow, reinterpret_cast<double*>(dense.get()));
+  if (reference == nullptr)
+    return Dataset::FromDenseMatrix(dense.get(), data_type, static_cast<int32_t>(nrow), static_cast<int32_t>(ncol), true, config);
+  return Dataset::FromDenseMatrixAligned(dense.get(), data_type, static_cast<int32_t>(nrow), static_cast<int32_t>(ncol), true,
+                                         *reinterpret_cast<const Dataset*>(reference), config);
+}
+
+}  // namespace
+
 extern "C" {
 
 const char* LGBM_GetLastError(void) { return g_last_error; }
@@ -137,6 +208,26 @@ int LGBM_DatasetCreateFromMat(const void* data, int data_type, int32_t nrow, int
     *out = Dataset::FromDenseMatrixAligned(data, data_type, nrow, ncol, is_row_major != 0,
                                            *reinterpret_cast<const Dataset*>(reference), config);
   }
+  API_END();
+}
+
+int LGBM_DatasetCreateFromCSR(const void* indptr, int indptr_type, const int32_t* indices, const void* data, int data_type,
+                              int64_t nindptr, int64_t nelem, int64_t num_col, const char* parameters,
+                              const DatasetHandle reference, DatasetHandle* out) {
+  API_BEGIN();
+  (void)nelem;
+  if (!out) Log::Fatal("LGBM_DatasetCreateFromCSR: NULL argument");
+  *out = DatasetFromSparse(true, indptr, indptr_type, indices, data, data_type, nindptr, nindptr - 1, num_col, parameters, reference);
+  API_END();
+}
+
+int LGBM_DatasetCreateFromCSC(const void* col_ptr, int col_ptr_type, const int32_t* indices, const void* data, int data_type,
+                              int64_t ncol_ptr, int64_t nelem, int64_t num_row, const char* parameters,
+                              const DatasetHandle reference, DatasetHandle* out) {
+  API_BEGIN();
+  (void)nelem;
+  if (!out) Log::Fatal("LGBM_DatasetCreateFromCSC: NULL argument");
+  *out = DatasetFromSparse(false, col_ptr, col_ptr_type, indices, data, data_type, ncol_ptr, num_row, ncol_ptr - 1, parameters, reference);
   API_END();
 }
 
@@ -528,6 +619,31 @@ int LGBM_BoosterFeatureImportance(BoosterHandle handle, int num_iteration, int i
     imp = b->gbdt->FeatureImportance(num_iteration, importance_type);
   }
   for (size_t i = 0; i < imp.size(); ++i) out_results[i] = imp[i];
+  API_END();
+}
+
+// LGBM_BoosterPredictForCSR (src/c_api.cpp:1893-1943): rows densified in chunks and sent through the dense prediction
+int LGBM_BoosterPredictForCSR(BoosterHandle handle, const void* indptr, int indptr_type, const int32_t* indices, const void* data,
+                              int data_type, int64_t nindptr, int64_t nelem, int64_t num_col, int predict_type, int start_iteration,
+                              int num_iteration, const char* parameter, int64_t* out_len, double* out_result) {
+  API_BEGIN();
+  (void)nelem;
+  if (!indptr || !indices || !data || !out_len || !out_result || num_col <= 0 || num_col >= INT32_MAX || nindptr < 1)
+    Log::Fatal("LGBM_BoosterPredictForCSR: bad argument");
+  const int64_t nrow = nindptr - 1;
+  const int64_t chunk = std::max<int64_t>(1, std::min<int64_t>(nrow, (static_cast<int64_t>(256) << 20) / (8 * num_col)));
+  std::vector<double> dense(static_cast<size_t>(chunk) * num_col);
+  int64_t total = 0;
+  for (int64_t r0 = 0; r0 < nrow; r0 += chunk) {
+    const int64_t rows = std::min(chunk, nrow - r0);
+    Densify<double>(true, indptr, indptr_type, indices, data, data_type, nindptr, nrow, num_col, r0, rows, dense.data());
+    int64_t len = 0;
+    if (LGBM_BoosterPredictForMat(handle, dense.data(), C_API_DTYPE_FLOAT64, static_cast<int32_t>(rows), static_cast<int32_t>(num_col), 1,
+                                  predict_type, start_iteration, num_iteration, parameter, &len, out_result + total) != 0)
+      throw std::runtime_error(LGBM_GetLastError());
+    total += len;
+  }
+  *out_len = total;
   API_END();
 }
 

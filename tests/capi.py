@@ -37,6 +37,33 @@ class LGBMLib:
             reference, C.byref(h)))
         return h
 
+    def dataset_from_sparse(self, S, params="", reference=None):
+        """S: scipy.sparse csr_matrix or csc_matrix (LGBM_DatasetCreateFromCSR / LGBM_DatasetCreateFromCSC)"""
+        csr = S.format == "csr"
+        assert csr or S.format == "csc"
+        ptr = np.ascontiguousarray(S.indptr); idx = np.ascontiguousarray(S.indices, dtype=np.int32)
+        val = np.ascontiguousarray(S.data)
+        assert ptr.dtype in (np.int32, np.int64) and val.dtype in (np.float32, np.float64)
+        h = C.c_void_p()
+        fn = self.lib.LGBM_DatasetCreateFromCSR if csr else self.lib.LGBM_DatasetCreateFromCSC
+        self.check(fn(ptr.ctypes.data_as(C.c_void_p), C.c_int(DTYPE_I32 if ptr.dtype == np.int32 else 3),
+                      idx.ctypes.data_as(C.POINTER(C.c_int32)), val.ctypes.data_as(C.c_void_p),
+                      C.c_int(DTYPE_F32 if val.dtype == np.float32 else DTYPE_F64), C.c_int64(len(ptr)), C.c_int64(len(val)),
+                      C.c_int64(S.shape[1] if csr else S.shape[0]), C.c_char_p(params.encode()), reference, C.byref(h)))
+        return h
+
+    def predict_csr(self, b, S, raw=False, num_class=1):
+        ptr = np.ascontiguousarray(S.indptr); idx = np.ascontiguousarray(S.indices, dtype=np.int32)
+        val = np.ascontiguousarray(S.data, dtype=np.float64)
+        out = np.empty(S.shape[0] * num_class, dtype=np.float64); n = C.c_int64()
+        self.check(self.lib.LGBM_BoosterPredictForCSR(
+            b, ptr.ctypes.data_as(C.c_void_p), C.c_int(DTYPE_I32 if ptr.dtype == np.int32 else 3),
+            idx.ctypes.data_as(C.POINTER(C.c_int32)), val.ctypes.data_as(C.c_void_p), C.c_int(DTYPE_F64), C.c_int64(len(ptr)),
+            C.c_int64(len(val)), C.c_int64(S.shape[1]), C.c_int(1 if raw else 0), C.c_int(0), C.c_int(-1), C.c_char_p(b""),
+            C.byref(n), out.ctypes.data_as(C.POINTER(C.c_double))))
+        assert n.value == len(out)
+        return out
+
     def set_field(self, ds, name, arr):
         arr = np.ascontiguousarray(arr)
         t = {np.dtype(np.float32): DTYPE_F32, np.dtype(np.float64): DTYPE_F64, np.dtype(np.int32): DTYPE_I32}[arr.dtype]

@@ -82,3 +82,29 @@ def test_validation_set_beside_bundled_training_data():
             lib.update(b)
         out[name] = lib.get_eval(b, 1)[0]
     assert abs(out["ref"] - out["ours"]) <= 1e-9
+
+
+def test_training_from_csr_and_csr_prediction():
+    """LGBM_DatasetCreateFromCSR / LGBM_BoosterPredictForCSR (densified on the host, then the dense path): the reference
+    trained from the same CSR matrix gives the same trees; predictions from CSR equal predictions from the dense matrix."""
+    sp = pytest.importorskip("scipy.sparse")
+    n = 30_000
+    X = np.nan_to_num(sparse_matrix(6, n, dtype=np.float64))
+    z = target(X, np.random.default_rng(61))
+    y = (z > np.median(z)).astype(np.float32)
+    S = sp.csr_matrix(X)
+    params = "objective=binary num_leaves=31 min_data_in_leaf=20 verbosity=-1"
+    out = {}
+    for name, lib, extra in (("ref", capi.reference(), " force_col_wise=true num_threads=4"), ("ours", capi.ours(), "")):
+        ds = lib.dataset_from_sparse(S, params + extra)
+        lib.set_field(ds, "label", y)
+        b = lib.booster_create(ds, params + extra)
+        for _ in range(8):
+            lib.update(b)
+        out[name] = (lib, b)
+    (ref, br), (ours, bo) = out["ref"], out["ours"]
+    assert_same_model(ref, ours, br, bo)
+    Sv = sp.csr_matrix(np.nan_to_num(sparse_matrix(7, 5000, dtype=np.float64)))
+    a = ref.predict_csr(br, Sv); b = ours.predict_csr(bo, Sv); c = ours.predict_mat(bo, Sv.toarray())
+    assert np.max(np.abs(a - b)) <= 1e-12
+    assert np.array_equal(b, c)

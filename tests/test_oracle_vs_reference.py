@@ -449,3 +449,42 @@ def test_categorical_features_bin_like_the_reference(shim, ref, ours, seed, n, e
         shim.ref_feature_bin_column(dr, C.c_int(f), want.ctypes.data_as(C.POINTER(C.c_int32)))
         assert np.array_equal(bins[:, f], want), f"inner feature {f} (column {real[f]}): bins differ"
     ref.dataset_free(dr); ours.dataset_free(do)
+
+
+@pytest.mark.parametrize("fmt,dtype,ptr", [("csr", np.float64, np.int32), ("csr", np.float32, np.int64), ("csc", np.float64, np.int32)])
+def test_sparse_input_bins_like_the_reference(shim, ref, ours, fmt, dtype, ptr, monkeypatch):
+    # LGBM_DatasetCreateFromCSR / CSC: the reference samples and pushes a sparse source to the same dataset as the dense
+    # matrix; this library densifies.  Every row's bins must equal the reference's own sparse-built dataset.
+    sp = pytest.importorskip("scipy.sparse")
+    monkeypatch.setenv("LGBM_B200_HOST_BINNING", "1")
+    n = 20_000
+    X = sparse_matrix(4, n, dtype=np.float64)
+    X = np.nan_to_num(X)                      # (a stored NaN is kept by both; absent = 0)
+    X[::97, 3] = np.nan
+    S = (sp.csr_matrix(X) if fmt == "csr" else sp.csc_matrix(X)).astype(dtype)
+    S.indptr = S.indptr.astype(ptr)
+    # (a CSC source is pushed column by column on parallel threads in the reference, so WHICH member of a bundle survives
+    # a conflicting row depends on thread timing there: the CSC case runs without bundling)
+    p = "max_bin=255 verbosity=-1" + (" enable_bundle=false" if fmt == "csc" else "")
+    dr = ref.dataset_from_sparse(S, p); do = ours.dataset_from_sparse(S, p)
+    nf = shim.ref_num_inner_features(dr)
+    nfo = C.c_int(); ours.check(ours.lib.LGBM_B200_DatasetNumInnerFeatures(do, C.byref(nfo)))
+    assert nfo.value == nf
+    bins = np.empty((n, nf), dtype=np.int32); real = np.empty(nf, dtype=np.int32)
+    ours.check(ours.lib.LGBM_B200_DatasetDumpBins(do, bins.ctypes.data_as(C.POINTER(C.c_int32)), real.ctypes.data_as(C.POINTER(C.c_int32))))
+    for f in range(nf):
+        mr = (C.c_int32 * 5)(); br = (C.c_double * 300)()
+        shim.ref_feature_info(dr, C.c_int(f), mr, br, C.c_int(300))
+        assert mr[4] == real[f]
+        want = np.empty(n, dtype=np.int32)
+        shim.ref_feature_bin_column(dr, C.c_int(f), want.ctypes.data_as(C.POINTER(C.c_int32)))
+        assert np.array_equal(bins[:, f], want), f"inner feature {f} (column {real[f]}): bins differ"
+    # an aligned dataset from a sparse source
+    Sv = sp.csr_matrix(np.nan_to_num(sparse_matrix(5, 3000, dtype=np.float64)))
+    dvr = ref.dataset_from_sparse(Sv, p, reference=dr); dvo = ours.dataset_from_sparse(Sv, p, reference=do)
+    bv = np.empty((3000, nf), dtype=np.int32)
+    ours.check(ours.lib.LGBM_B200_DatasetDumpBins(dvo, bv.ctypes.data_as(C.POINTER(C.c_int32)), real.ctypes.data_as(C.POINTER(C.c_int32))))
+    for f in range(nf):
+        want = np.empty(3000, dtype=np.int32)
+        shim.ref_feature_bin_column(dvr, C.c_int(f), want.ctypes.data_as(C.POINTER(C.c_int32)))
+        assert np.array_equal(bv[:, f], want)
