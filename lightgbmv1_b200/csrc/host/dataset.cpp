@@ -49,8 +49,26 @@ int ConflictCount(const std::vector<bool>& mark, const std::vector<int>& idx, in
   return ret;
 }
 
+// (The conflict marks of a group are only needed when a later feature is tried against it.  With dense features no group
+// is ever available to a later feature, so the marks -- one bit per sampled row and feature -- are built on first
+// use instead of up front: 17 ms less at 28 dense features x 200K samples.)
+struct GroupMarks {
+  std::vector<std::vector<bool>> marks;      // empty vector = not materialised yet
+  const std::vector<const std::vector<int>*>* nz;
+  const std::vector<std::vector<int>>* groups;
+  int total;
+  std::vector<bool>& get(int g) {
+    if (marks[g].empty()) {
+      marks[g].assign(total, false);
+      for (int f : (*groups)[g]) for (int i : *(*nz)[f]) marks[g][i] = true;
+    }
+    return marks[g];
+  }
+  void add(int g, int f) { if (!marks[g].empty()) for (int i : *(*nz)[f]) marks[g][i] = true; }
+};
+
 std::vector<std::vector<int>> FindGroups(const std::vector<std::shared_ptr<BinMapper>>& mappers,
-                                         const std::vector<int>& order, const std::vector<std::vector<int>>& nz_idx,
+                                         const std::vector<int>& order, const std::vector<const std::vector<int>*>& nz_idx,
                                          int total_sample_cnt, data_size_t num_data, bool is_sparse,
                                          std::vector<int8_t>* multi_val) {
   const int max_search_group = 100;
@@ -58,10 +76,10 @@ std::vector<std::vector<int>> FindGroups(const std::vector<std::shared_ptr<BinMa
   multi_val->clear();
   Random rand(num_data);
   std::vector<std::vector<int>> groups;
-  std::vector<std::vector<bool>> marks;
+  GroupMarks gm; gm.nz = &nz_idx; gm.groups = &groups; gm.total = total_sample_cnt;
   std::vector<int> used_rows, total_cnt, group_bins;
   for (int f : order) {
-    const int nz = static_cast<int>(nz_idx[f].size());
+    const int nz = static_cast<int>(nz_idx[f]->size());
     std::vector<int> avail;
     for (int g = 0; g < static_cast<int>(groups.size()); ++g) {
       if (total_cnt[g] + nz <= total_sample_cnt + max_conflict) avail.push_back(g);
@@ -76,19 +94,18 @@ std::vector<std::vector<int>> FindGroups(const std::vector<std::shared_ptr<BinMa
     int best = -1, best_conf = -1;
     for (int g : search) {
       const int rest = max_conflict - total_cnt[g] + used_rows[g];
-      const int cnt = ConflictCount(marks[g], nz_idx[f], rest);
+      const int cnt = ConflictCount(gm.get(g), *nz_idx[f], rest);
       if (cnt >= 0 && cnt <= rest && cnt <= nz / 2) { best = g; best_conf = cnt; break; }
     }
     if (best >= 0) {
+      gm.add(best, f);   // (before the push: a materialised mark set is complete up to here)
       groups[best].push_back(f);
       total_cnt[best] += nz;
       used_rows[best] += nz - best_conf;
-      for (int i : nz_idx[f]) marks[best][i] = true;
       group_bins[best] += mappers[f]->num_bin() + (mappers[f]->default_bin() == 0 ? -1 : 0);
     } else {
       groups.emplace_back(1, f);
-      marks.emplace_back(total_sample_cnt, false);
-      for (int i : nz_idx[f]) marks.back()[i] = true;
+      gm.marks.emplace_back();
       total_cnt.push_back(nz);
       used_rows.push_back(nz);
       group_bins.push_back(1 + mappers[f]->num_bin() + (mappers[f]->default_bin() == 0 ? -1 : 0));
@@ -97,10 +114,10 @@ std::vector<std::vector<int>> FindGroups(const std::vector<std::shared_ptr<BinMa
   if (!is_sparse) { multi_val->assign(groups.size(), 0); return groups; }
   std::vector<int> second;
   std::vector<std::vector<int>> groups2;
-  std::vector<std::vector<bool>> marks2;
+  std::vector<std::vector<bool>> marks2;   // (the second round never reads the kept groups' marks)
   for (size_t g = 0; g < groups.size(); ++g) {
     const double dense_rate = static_cast<double>(used_rows[g]) / total_sample_cnt;
-    if (dense_rate >= 0.4) { groups2.push_back(std::move(groups[g])); marks2.push_back(std::move(marks[g])); }
+    if (dense_rate >= 0.4) { groups2.push_back(std::move(groups[g])); }
     else for (int f : groups[g]) second.push_back(f);
   }
   groups = groups2;
@@ -114,10 +131,10 @@ std::vector<std::vector<int>> FindGroups(const std::vector<std::shared_ptr<BinMa
       groups.back().push_back(f);
       if (!is_multi) {
         const int rest = max_conflict - conflicts;
-        const int cnt = ConflictCount(mark, nz_idx[f], rest);
+        const int cnt = ConflictCount(mark, *nz_idx[f], rest);
         conflicts += cnt;
         if (cnt < 0 || conflicts > max_conflict) { is_multi = true; continue; }
-        for (int i : nz_idx[f]) mark[i] = true;
+        for (int i : *nz_idx[f]) mark[i] = true;
       }
     }
     multi_val->push_back(is_multi ? 1 : 0);
@@ -129,13 +146,16 @@ std::vector<std::vector<int>> FindGroups(const std::vector<std::shared_ptr<BinMa
 // `bundle_of_real`: per raw column, 0 or the 1-based id of the single-column bundle it belongs to
 std::vector<int> BundledFeatureOrder(const std::vector<std::shared_ptr<BinMapper>>& mappers,
                                      const std::vector<int>& used, const std::vector<std::vector<double>>& sample_vals,
-                                     std::vector<std::vector<int>> sample_idx, int total_sample_cnt, data_size_t num_data,
+                                     const std::vector<std::vector<int>>& sample_idx, int total_sample_cnt, data_size_t num_data,
                                      std::vector<int>* bundle_of_real) {
   // FixSampleIndices: when the most frequent bin is not the zero bin, "non-zero" means "not in the most frequent bin"
+  std::vector<const std::vector<int>*> nz(sample_idx.size(), nullptr);
+  std::vector<std::vector<int>> fixed_lists(sample_idx.size());
+  for (size_t f = 0; f < sample_idx.size(); ++f) nz[f] = &sample_idx[f];
   for (int f : used) {
     const BinMapper& m = *mappers[f];
     if (m.default_bin() == m.most_freq_bin()) continue;
-    std::vector<int> fixed;
+    std::vector<int>& fixed = fixed_lists[f];
     const auto& idx = sample_idx[f];
     const auto& val = sample_vals[f];
     int i = 0; size_t j = 0;
@@ -147,17 +167,17 @@ std::vector<int> BundledFeatureOrder(const std::vector<std::shared_ptr<BinMapper
       } else fixed.push_back(i++);
     }
     // an empty result means "keep the original list" in the reference (it tests ret.empty())
-    if (!fixed.empty()) sample_idx[f] = fixed;
+    if (!fixed.empty()) nz[f] = &fixed;
   }
   std::vector<int> by_cnt(used.size());
   for (size_t i = 0; i < used.size(); ++i) by_cnt[i] = static_cast<int>(i);
   // NOTE the reference sorts by the ORIGINAL non-zero counts (num_per_col), not the fixed ones; ordering only
   // matters when it yields fewer groups, which for one-feature groups it never does.
   std::vector<int8_t> mv1, mv2;
-  auto g1 = FindGroups(mappers, used, sample_idx, total_sample_cnt, num_data, true, &mv1);
+  auto g1 = FindGroups(mappers, used, nz, total_sample_cnt, num_data, true, &mv1);
   std::vector<int> order2(used);
   std::stable_sort(order2.begin(), order2.end(), [&](int a, int b) { return sample_vals[a].size() > sample_vals[b].size(); });
-  auto g2 = FindGroups(mappers, order2, sample_idx, total_sample_cnt, num_data, true, &mv2);
+  auto g2 = FindGroups(mappers, order2, nz, total_sample_cnt, num_data, true, &mv2);
   if (g1.size() > g2.size()) { g1 = g2; mv1 = mv2; }
   const int ng = static_cast<int>(g1.size());
   Random shuffle(num_data);
@@ -209,14 +229,49 @@ Dataset* Dataset::FromDenseMatrix(const void* data, int data_type, int32_t nrow,
     }
   }
   st.tick("sample gather");
+  if (row_major) {
+    // Every thread takes a contiguous range of the samples and walks its rows of the block once, all columns (a column
+    // at a time over the whole block reads every cache line of it once per column: 30 ms instead of 4 at 200K x 28):
+    // first the non-zero counts per (thread, column), then each thread writes its entries behind those of the
+    // threads before it -- the lists come out in sample order, as the reference's row-by-row loop produces them.
+    const int T = std::max(1, omp_get_max_threads());
+    std::vector<int> cnt(static_cast<size_t>(T + 1) * ncol, 0);
+    auto keep = [](double v) { return std::fabs(v) > kZeroThreshold || std::isnan(v); };
+#pragma omp parallel num_threads(T)
+    {
+      const int t = omp_get_thread_num(), nt = omp_get_num_threads();   // (the runtime may grant fewer than T threads)
+      const int i0 = static_cast<int>(static_cast<int64_t>(sample_cnt) * t / nt), i1 = static_cast<int>(static_cast<int64_t>(sample_cnt) * (t + 1) / nt);
+      int* my = cnt.data() + static_cast<size_t>(t + 1) * ncol;
+      for (int i = i0; i < i1; ++i) {
+        const double* row = block.get() + static_cast<size_t>(i) * ncol;
+        for (int c = 0; c < ncol; ++c) my[c] += keep(row[c]) ? 1 : 0;
+      }
+#pragma omp barrier
+#pragma omp for schedule(static)
+      for (int c = 0; c < ncol; ++c) {   // exclusive prefix over the threads, per column; the lists get their final size
+        int run = 0;
+        for (int k = 1; k <= nt; ++k) { const int v = cnt[static_cast<size_t>(k) * ncol + c]; cnt[static_cast<size_t>(k) * ncol + c] = run; run += v; }
+        sample_vals[c].resize(run); sample_idx[c].resize(run);
+      }
+      // (implicit barrier of the omp for)
+      std::vector<int> pos(my, my + ncol);
+      for (int i = i0; i < i1; ++i) {
+        const double* row = block.get() + static_cast<size_t>(i) * ncol;
+        for (int c = 0; c < ncol; ++c) {
+          if (keep(row[c])) { sample_vals[c][pos[c]] = row[c]; sample_idx[c][pos[c]] = i; ++pos[c]; }
+        }
+      }
+    }
+  } else {
 #pragma omp parallel for schedule(dynamic)
-  for (int c = 0; c < ncol; ++c) {
-    sample_vals[c].reserve(sample_cnt); sample_idx[c].reserve(sample_cnt);
-    for (int i = 0; i < sample_cnt; ++i) {
-      const double v = row_major ? block[static_cast<size_t>(i) * ncol + c] : M.at(sample[i], c);
-      if (std::fabs(v) > kZeroThreshold || std::isnan(v)) {
-        sample_vals[c].push_back(v);
-        sample_idx[c].push_back(i);
+    for (int c = 0; c < ncol; ++c) {
+      sample_vals[c].reserve(sample_cnt); sample_idx[c].reserve(sample_cnt);
+      for (int i = 0; i < sample_cnt; ++i) {
+        const double v = M.at(sample[i], c);
+        if (std::fabs(v) > kZeroThreshold || std::isnan(v)) {
+          sample_vals[c].push_back(v);
+          sample_idx[c].push_back(i);
+        }
       }
     }
   }
