@@ -371,13 +371,74 @@ __global__ void __cluster_dims__(HIST_CLUSTER, 1, 1) __launch_bounds__(HIST_THRE
 }
 
 
-// The same launch for data with a wide feature: no clusters, no sub-histograms (hist_global_wide_path).
-__global__ void __launch_bounds__(256) k_hist_wide(DevView V, int leaf_arg) {
+// The same launch for data with a wide feature.  k_hist's scheme -- a block-shared sub-histogram of 256 bins x 32
+// features, lane = feature -- does not stretch to thousands of bins, so here a block takes ONE feature and a slice of
+// the leaf's rows: the feature's whole histogram (16 bytes per slot, `smem_slots` of them fit) lives in shared memory as
+// (low word, high word) pairs per sum, the rows' bins come from the column-major copy (both bytes of a wide feature,
+// coalesced for the full-data root pass), a row's value is added with a 32-bit shared atomic per word and the carry
+// handed to the high word -- the same exact 64-bit integer sums as everywhere -- and the block flushes its non-zero
+// slots to the leaf's pool slot with global atomics.  Leaves too small to amortise zeroing and flushing, and features with
+// more slots than fit, take the global-atomic path (hist_global_wide_path).  Measured at 2M x 28, max_bin = 1023:
+// 2.5 ms of histogram time per iteration against 10.2 ms with global atomics alone (the 8-bit kernel: 0.74 ms at 255 bins).
+#define WIDE_HIST_MIN_ELEMS 32768   /* rows x features below which a leaf goes straight to global atomics */
+__device__ __forceinline__ void wide_add64(unsigned* w, i64 v) {   // w[0] low word, w[1] high word
+  const unsigned lo = (unsigned)v;
+  const unsigned old = atomicAdd(&w[0], lo);
+  const unsigned carry = (old + lo) < old ? 1u : 0u;
+  const unsigned hi = (unsigned)((unsigned long long)v >> 32) + carry;
+  if (hi) atomicAdd(&w[1], hi);
+}
+
+__global__ void __launch_bounds__(256) k_hist_wide(DevView V, int leaf_arg, int smem_slots) {
+  extern __shared__ __align__(16) unsigned wide_smem[];   // [slots][4]: g low, g high, h low, h high
   STAMP(V.ctl, 0);
   DevLeaf L; bool is_root; int bid, nblocks;
   if (!hist_pick_work(V, leaf_arg, 1, &L, &is_root, &bid, &nblocks)) return;
   const bool identity = V.ctl->root_identity && is_root && L.count == V.num_data;
-  hist_global_wide_path(V, L, identity, bid, nblocks);
+  const int F = V.num_features, tid = threadIdx.x;
+  if ((long long)L.count * F < WIDE_HIST_MIN_ELEMS) {
+    hist_global_wide_path(V, L, identity, bid, nblocks);
+  } else {
+    const int* idx = V.indices[L.buf] + L.begin;
+    const double scale_g = V.ctl->scale_g, scale_h = V.ctl->scale_h;
+    int slices = nblocks / F; if (slices < 1) slices = 1;
+    const int units = F * slices;
+    const int rows_per_slice = (L.count + slices - 1) / slices;
+    for (int u = bid; u < units; u += nblocks) {
+      const int f = u % F, sl = u / F;   // neighbouring blocks: the same rows, different features (the gh records stay in L2)
+      const DevFeat Ft = V.feats[f];
+      const int r0 = sl * rows_per_slice, r1 = min(L.count, r0 + rows_per_slice);
+      const uint8_t* col = V.bins_col + (size_t)Ft.col * V.col_stride;
+      HistEntry* out = V.hist_pool + (size_t)L.slot * V.total_bin + Ft.hist_base;
+      if (Ft.nslots > smem_slots) {      // does not fit: global atomics for this (feature, slice)
+        for (int p = r0 + tid; p < r1; p += blockDim.x) {
+          const int row = identity ? p : idx[p];
+          int b = col[row]; if (Ft.wide) b |= (int)col[row + V.col_stride] << 8;
+          const float2 gh = V.gh[row];
+          atomic_add_i64(&out[b].g, to_fixed(gh.x, scale_g));
+          atomic_add_i64(&out[b].h, to_fixed(gh.y, scale_h));
+        }
+        continue;
+      }
+      for (int i = tid; i < Ft.nslots * 4; i += blockDim.x) wide_smem[i] = 0u;
+      __syncthreads();
+      for (int p = r0 + tid; p < r1; p += blockDim.x) {
+        const int row = identity ? p : idx[p];
+        int b = col[row]; if (Ft.wide) b |= (int)col[row + V.col_stride] << 8;
+        const float2 gh = V.gh[row];
+        wide_add64(&wide_smem[b * 4], to_fixed(gh.x, scale_g));
+        wide_add64(&wide_smem[b * 4 + 2], to_fixed(gh.y, scale_h));
+      }
+      __syncthreads();
+      for (int b = tid; b < Ft.nslots; b += blockDim.x) {
+        const i64 g = (i64)(((unsigned long long)wide_smem[b * 4 + 1] << 32) | wide_smem[b * 4]);
+        const i64 h = (i64)(((unsigned long long)wide_smem[b * 4 + 3] << 32) | wide_smem[b * 4 + 2]);
+        if (g) atomic_add_i64(&out[b].g, g);
+        if (h) atomic_add_i64(&out[b].h, h);
+      }
+      __syncthreads();
+    }
+  }
   if (bid == 0 && threadIdx.x == 0) {
     atomicAdd(&V.ctl->prof_hist_calls, 1ull);
     atomicAdd(identity ? &V.ctl->prof_hist_rows : &V.ctl->prof_hist_rows_indexed, (unsigned long long)L.count);

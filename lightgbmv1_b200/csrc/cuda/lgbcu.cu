@@ -220,6 +220,7 @@ struct LgbCuContext {
   bool any_cat = false, general = false; int cat_features = 0;
   // monotone constraints (basic method): per-feature types on the device; every feature then takes the general search
   bool use_mc = false; signed char* d_monotone = nullptr; double mc_penalty = 0.0;
+  int wide_smem_slots = 0;   // slots of a feature's histogram that k_hist_wide keeps in shared memory
   unsigned* d_cat_pool = nullptr; int cat_cap = 0;
   unsigned* d_tree_cat = nullptr; int tree_cat_count = 0, tree_cat_cap = 0;
   DevCatParams cat_params{10.0, 10.0, 32, 100, 4, 0};
@@ -395,7 +396,7 @@ int ensure_tree_buffers(LgbCuContext* c) {
 
 int launch_hist(LgbCuContext* c, int leaf_arg) {
   const DevView V = c->view();
-  if (c->any_wide) LAUNCH(k_hist_wide, c->num_sms * 8, 256, 0, c->stream, V, leaf_arg);
+  if (c->any_wide) LAUNCH(k_hist_wide, c->num_sms * 8, 256, (size_t)c->wide_smem_slots * 16, c->stream, V, leaf_arg, c->wide_smem_slots);
   else LAUNCH(k_hist, c->hist_grid, HIST_THREADS, HIST_SMEM_BYTES, c->stream, V, leaf_arg, c->hist_mode, c->hist_min_rows, c->hist_small_rows);
   CU(cudaGetLastError());
   return 0;
@@ -782,6 +783,14 @@ static int setup_dataset_common(LgbCuContext* c, int32_t num_data, int32_t num_f
   {
     c->use_mc = false;   // lgbcu_set_monotone follows the dataset
     c->general = c->any_wide || c->any_cat;
+    if (c->any_wide) {
+      // k_hist_wide: the largest feature's histogram in shared memory if it fits (16 bytes a slot, 192 KB at most, and
+      // small enough for several blocks per SM when the features allow it)
+      int max_slots = 0;
+      for (int f = 0; f < num_features; ++f) max_slots = std::max(max_slots, c->h_feats[f].nslots);
+      c->wide_smem_slots = std::min(max_slots, 12288);
+      CU(cudaFuncSetAttribute(k_hist_wide, cudaFuncAttributeMaxDynamicSharedMemorySize, c->wide_smem_slots * 16));
+    }
     const int fb = c->general ? KEY_FEAT_BITS_WIDE : KEY_FEAT_BITS;
     NEED(num_features < (1 << fb), "lgbcu_set_dataset: %d features exceed the supported %d%s", num_features, (1 << fb) - 1,
          c->general ? " (for data with a categorical feature or more than 256 bins in a feature)" : "");
