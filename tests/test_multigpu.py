@@ -26,9 +26,11 @@ GOLDEN = os.path.join(H.ROOT, "tests", "golden", "dp_reference_2rank_model.txt")
 SCRIPT = os.path.join(H.ROOT, "tools", "run_dp.py")
 
 
-def _torchrun(nproc, port, out, extra="", sorted_shards=False, env=None):
+def _torchrun(nproc, port, out, extra="", sorted_shards=False, env=None, max_bin=0):
     cmd = [sys.executable, "-m", "torch.distributed.run", "--nnodes=1", f"--nproc-per-node={nproc}",
            "--master-addr", "127.0.0.1", "--master-port", str(port), SCRIPT, "--out", out]
+    if max_bin:
+        cmd += ["--max-bin", str(max_bin)]
     if extra:
         cmd += ["--extra", extra]
     if sorted_shards:
@@ -101,6 +103,23 @@ def test_two_rank_one_shot_exchange(tmp_path, sorted_shards, form):
         _assert_same(open(GOLDEN).read(), b, "reference 2-machine socket run vs 2-rank run with the one-shot exchange")
     same, n, first = capi.compare_models(a, b, rtol_value=0.0)
     assert same == n, (same, n, first)
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("env", [{}, {"LGBCU_DP_OWNERSHIP": "1"}, {"LGBCU_DP_ONESHOT": "0"}])
+def test_two_rank_wide_features_equal_one_rank(tmp_path, env):
+    """max_bin = 1000 under tree_learner=data: the wide histogram kernel adds into the exchanged pool, the general split
+    search runs on the reduced histograms (in every exchange form) -- integer sums, so the 2-rank model must equal the
+    1-rank model with the data-parallel count semantics bit for bit."""
+    if N.device_count() < 2:
+        pytest.skip("needs 2 GPUs")
+    one, two = str(tmp_path / "one.txt"), str(tmp_path / "two.txt")
+    subprocess.check_call([sys.executable, SCRIPT, "--out", one, "--max-bin", "1000"], env=dict(os.environ, LGBCU_FORCE_DP_COUNTS="1"), timeout=600)
+    _torchrun(2, 29531 + len(env) + 2 * ("LGBCU_DP_ONESHOT" in env), two, env=env, max_bin=1000)
+    a, b = open(one).read(), open(two).read()
+    same, n, first = capi.compare_models(a, b, rtol_value=0.0)
+    assert same == n, (same, n, first)
+    assert "max_bin: 1000" in a
 
 
 @pytest.mark.gpu

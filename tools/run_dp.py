@@ -13,6 +13,7 @@ import make_dp_golden as G
 ap = argparse.ArgumentParser()
 ap.add_argument("--out", default="")
 ap.add_argument("--extra", default="", help="extra parameters, e.g. is_unbalance=true")
+ap.add_argument("--max-bin", type=int, default=0, help="replace the case's max_bin (e.g. 1000: wide features)")
 ap.add_argument("--iters", type=int, default=G.ITERS)
 ap.add_argument("--sorted-shards", action="store_true", help="rows sorted by a feature: skewed shards, empty local leaves")
 args = ap.parse_args()
@@ -22,6 +23,8 @@ X, y, ref_rows = G.dp_case(sorted_shards=args.sorted_shards)
 n = len(y)
 ours = capi.ours(); lib = ours.lib
 base = G.BASE + (" " + args.extra if args.extra else "")
+if args.max_bin:
+    base = base.replace("max_bin=255", f"max_bin={args.max_bin}")
 ref_ds = ours.dataset_from_mat(np.ascontiguousarray(X[ref_rows]), base + f" gpu_device_id={local}")
 if world > 1:
     import torch, torch.distributed as dist
