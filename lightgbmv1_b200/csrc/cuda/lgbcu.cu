@@ -561,6 +561,9 @@ int setup_ownership(LgbCuContext* c) {
   if (c->dp_owner_cfg == 1) want = c->comm != nullptr && c->world > 1;
   if (want && !g_nccl.has_ownership_calls()) want = false;
   if (want && c->F < c->world) want = false;
+  // a categorical winner names its bin set by an index into the RANK's own pool: such records cannot be gathered from
+  // other ranks, so categorical data keeps the replicated search on the reduced histograms
+  if (want && c->any_cat) want = false;
   if (want == c->dp_owner && (!want || (int)c->own_begin.size() == c->world + 1)) return 0;
   drop_graph(c);
   c->dp_owner = want;
@@ -1172,7 +1175,6 @@ int lgbcu_set_monotone(LgbCuContext* c, const int8_t* types, int32_t num_feature
   if (!types) { c->use_mc = false; c->general = c->any_wide || c->any_cat; return 0; }
   NEED(num_features == c->F, "lgbcu_set_monotone: %d types for %d features", num_features, c->F);
   NEED(penalty >= 0.0, "lgbcu_set_monotone: monotone_penalty should be >= 0");
-  NEED(!c->comm, "lgbcu_set_monotone: monotone constraints with tree_learner=data are outside this library's path");
   for (int f = 0; f < num_features; ++f) {
     NEED(types[f] >= -1 && types[f] <= 1, "lgbcu_set_monotone: type of feature %d is %d", f, (int)types[f]);
     NEED(types[f] == 0 || !c->h_feats[f].cat, "The output cannot be monotone with respect to categorical features");

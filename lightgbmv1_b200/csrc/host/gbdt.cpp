@@ -88,14 +88,12 @@ GBDT::GBDT(const Dataset* train, const Config& config)
   tp.max_delta_step = config_.max_delta_step; tp.path_smooth = config_.path_smooth;
   Check(lgbcu_set_tree_params(ctx_, &tp));
   if (has_categorical_) {
-    if (data_parallel_) Log::Fatal("categorical features with tree_learner=data are outside this library's path");
     Check(lgbcu_set_cat_params(ctx_, config_.cat_smooth, config_.cat_l2, config_.max_cat_threshold, config_.min_data_per_group,
                                config_.max_cat_to_onehot));
   }
   if (!config_.monotone_constraints.empty()) {
     if (static_cast<int>(config_.monotone_constraints.size()) != train_->num_total_features())
       Log::Fatal("Check failed: (num_total_features_) == (io_config.monotone_constraints.size())");
-    if (data_parallel_) Log::Fatal("monotone constraints with tree_learner=data are outside this library's path");
     std::vector<int8_t> types(F);
     for (int f = 0; f < F; ++f) {
       types[f] = config_.monotone_constraints[train_->real_feature_index(f)];

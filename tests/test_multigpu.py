@@ -123,6 +123,27 @@ def test_two_rank_wide_features_equal_one_rank(tmp_path, env):
 
 
 @pytest.mark.gpu
+@pytest.mark.parametrize("extra,env", [("categorical_feature=25,26,27,0 max_cat_to_onehot=2 cat_smooth=1 min_data_per_group=10", {}),
+                                       ("categorical_feature=25,26,27,0 max_cat_to_onehot=2 cat_smooth=1 min_data_per_group=10", {"LGBCU_DP_ONESHOT": "0"}),
+                                       ("monotone_constraints=1,-1,0,0,0,0,0,0,0,0,0,0,0,0,0,0,0,0,0,0,0,0,0,0,0,0,0,0 monotone_penalty=0.5", {}),
+                                       ("monotone_constraints=1,-1,0,0,0,0,0,0,0,0,0,0,0,0,0,0,0,0,0,0,0,0,0,0,0,0,0,0", {"LGBCU_DP_OWNERSHIP": "1"})])
+def test_two_rank_categorical_and_monotone_equal_one_rank(tmp_path, extra, env):
+    """Categorical features and monotone constraints under tree_learner=data: every rank runs the general split search on
+    the same reduced histograms (a categorical split's bin set stays in the rank's own pool; feature ownership is not
+    used with categorical data), so the 2-rank model equals the 1-rank model with the data-parallel count semantics."""
+    if N.device_count() < 2:
+        pytest.skip("needs 2 GPUs")
+    one, two = str(tmp_path / "one.txt"), str(tmp_path / "two.txt")
+    subprocess.check_call([sys.executable, SCRIPT, "--out", one, "--extra", extra], env=dict(os.environ, LGBCU_FORCE_DP_COUNTS="1"), timeout=600)
+    _torchrun(2, 29541 + len(extra) % 7 + 3 * len(env), two, extra=extra, env=env)
+    a, b = open(one).read(), open(two).read()
+    same, n, first = capi.compare_models(a, b, rtol_value=0.0)
+    assert same == n, (same, n, first)
+    if "categorical" in extra:
+        assert any(int(t["num_cat"][0]) > 0 for t in capi.parse_trees(b)), "no categorical split in the case"
+
+
+@pytest.mark.gpu
 def test_two_rank_sorted_shards_is_unbalance_equals_one_rank(tmp_path):
     if N.device_count() < 2:
         pytest.skip("needs 2 GPUs")
