@@ -194,22 +194,33 @@ __device__ void wide_find_best_threshold_block(WideScratch& W, const WideData& D
 }
 
 // ---- categorical features -------------------------------------------------------------------------------------------
-// FeatureHistogram::FindBestThresholdCategoricalInner (feature_histogram.hpp:277-513; no monotone constraints, no
-// extra_trees) by ONE thread; G / H = data_[t] of the feature as doubles, staged in shared memory by the block (a walk that
-// fetches every entry from global memory spends 9/10 of its time waiting: 90 -> ~10 us per block at 50 categories).  One-hot (num_bin <= max_cat_to_onehot): every bin
-// against the rest.  Otherwise: the bins with enough data, stably sorted by sum_gradient / (sum_hessian + cat_smooth),
-// are accumulated from the low end and from the high end, up to max_cat_threshold bins a side.  `sorted` = scratch in
-// shared memory for 256 bin indices; `bits` = LGB_CAT_WORDS words that receive the set of BINS going left.
-__device__ void cat_find_best_threshold(const double* __restrict__ G, const double* __restrict__ H, const DevFeat& F, const DevParams& P0, const DevCatParams& C,
-                                        double sum_g, double leaf_sum_h, int num_data, double parent_output, const McInfo& M,
-                                        unsigned char* sorted, double* ctr, unsigned* bits, DevSplit* out, int* splittable_out) {
+// FeatureHistogram::FindBestThresholdCategoricalInner (feature_histogram.hpp:277-513; no extra_trees) by the block.
+// G / H = data_[t] of the feature as doubles, staged in shared memory.  One-hot (num_bin <= max_cat_to_onehot): every
+// bin against the rest, one thread per bin.  Otherwise: the bins with enough data are stably sorted by
+// sum_gradient / (sum_hessian + cat_smooth) -- a rank sort, one thread per bin -- and accumulated from the low end and
+// from the high end, up to max_cat_threshold bins a side: the accumulation with its `continue` / `break` tests and the
+// min_data_per_group counter is a short sequential state machine (one thread per direction, additions only) that
+// records the candidates it would score; the gains -- the expensive part -- are then computed side by side, and a block
+// arg-max keeps the first best in the reference's order (direction +1 before -1, then position).  `bits` receives the
+// set of BINS going left (thread 0's copy is the one used).
+struct CatScratch {
+  double ctr[256];
+  double cand_g[256], cand_h[256];   // [direction * 128 + position]: left sums of a candidate
+  int cand_c[256];
+  unsigned char sorted[256], tmp[256], cand_ok[256];
+  double wgain[FS_WARPS]; int wpos[FS_WARPS];
+  int used_bin;
+};
+
+__device__ void cat_find_best_threshold_block(CatScratch& K, const double* __restrict__ G, const double* __restrict__ H, const DevFeat& F,
+                                              const DevParams& P0, const DevCatParams& C, double sum_g, double leaf_sum_h, int num_data,
+                                              double parent_output, const McInfo& M, unsigned* bits, DevSplit* out, int* splittable_out) {
+  const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
   DevSplit o;
   o.gain = LGB_MIN_SCORE; o.feature = -1; o.real_feature = -1; o.threshold = 0; o.default_left = 0;
   o.left_count = 0; o.right_count = 0; o.left_output = 0; o.right_output = 0;
   o.left_sum_g = 0; o.left_sum_h = 0; o.right_sum_g = 0; o.right_sum_h = 0;
   const double sum_h = leaf_sum_h + (double)(2 * 1e-15f);
-  double best_gain = LGB_MIN_SCORE, best_lg = 0, best_lh = 0;
-  int best_lc = 0;
   double gain_shift;
   if (P0.use_smoothing) {
     const double sg = P0.use_l1 ? threshold_l1(sum_g, P0.lambda_l1) : sum_g;   // GetLeafGainGivenOutput
@@ -220,54 +231,68 @@ __device__ void cat_find_best_threshold(const double* __restrict__ G, const doub
   const double min_gain_shift = gain_shift + P0.min_gain_to_split;
   const int offset = F.offset;
   const int bin_start = 1 - offset, bin_end = F.num_bin - offset;
-  int used_bin = -1;
   DevParams P = P0;   // l2 grows by cat_l2 in the many-vs-many search
   const bool use_onehot = F.num_bin <= C.max_cat_to_onehot;
-  int best_threshold = -1, best_dir = 1;
   const double cnt_factor = num_data / sum_h;
-  int splittable = 0;
+  // this thread's candidate: (gain, left sums); `ok` = it beat min_gain_shift
+  double gain = LGB_MIN_SCORE, c_lg = 0, c_lh = 0; int c_lc = 0; bool ok = false;
+  int used_bin = 0;
   if (use_onehot) {
-    for (int t = bin_start; t < bin_end; ++t) {
+    const int t = bin_start + tid;
+    if (t < bin_end) {
       const double grad = G[t], hess = H[t];
       const int cnt = round_int(hess * cnt_factor);
-      if (cnt < P.min_data_in_leaf || hess < P.min_sum_hessian) continue;
       const int other_count = num_data - cnt;
-      if (other_count < P.min_data_in_leaf) continue;
       const double sum_other_h = sum_h - hess - LGB_EPS;
-      if (sum_other_h < P.min_sum_hessian) continue;
-      const double sum_other_g = sum_g - grad;
-      const double gain = mc_split_gains(sum_other_g, sum_other_h, grad, hess + LGB_EPS, P, other_count, cnt, parent_output, M);
-      if (gain <= min_gain_shift) continue;
-      splittable = 1;
-      if (gain > best_gain) { best_threshold = t; best_lg = grad; best_lh = hess + LGB_EPS; best_lc = cnt; best_gain = gain; }
-    }
-  } else {
-    used_bin = 0;
-    for (int i = bin_start; i < bin_end; ++i) {
-      if (round_int(H[i] * cnt_factor) >= C.cat_smooth) {
-        sorted[used_bin] = (unsigned char)i;
-        ctr[used_bin] = G[i] / (H[i] + C.cat_smooth);
-        ++used_bin;
+      if (!(cnt < P.min_data_in_leaf || hess < P.min_sum_hessian) && !(other_count < P.min_data_in_leaf) &&
+          !(sum_other_h < P.min_sum_hessian)) {
+        gain = mc_split_gains(sum_g - grad, sum_other_h, grad, hess + LGB_EPS, P, other_count, cnt, parent_output, M);
+        ok = gain > min_gain_shift;
+        c_lg = grad; c_lh = hess + LGB_EPS; c_lc = cnt;
       }
     }
+  } else {
     P.lambda_l2 += C.cat_l2;
-    // std::stable_sort by ctr ascending: an insertion sort is stable and the list is short (<= 255)
-    for (int i = 1; i < used_bin; ++i) {
-      const unsigned char bi = sorted[i]; const double ci = ctr[i];
-      int j = i - 1;
-      while (j >= 0 && ci < ctr[j]) { sorted[j + 1] = sorted[j]; ctr[j + 1] = ctr[j]; --j; }
-      sorted[j + 1] = bi; ctr[j + 1] = ci;
+    // the bins with enough data, in bin order (thread 0 compacts; the flags and ratios are computed side by side)
+    const int t = bin_start + tid;
+    bool use = false;
+    if (t < bin_end) { use = round_int(H[t] * cnt_factor) >= C.cat_smooth; K.ctr[tid] = use ? G[t] / (H[t] + C.cat_smooth) : 0.0; K.tmp[tid] = use ? 1 : 0; }
+    __syncthreads();
+    if (tid == 0) {
+      int n = 0;
+      for (int i = 0; i < bin_end - bin_start; ++i) if (K.tmp[i]) K.sorted[n++] = (unsigned char)i;   // position in the bin range
+      K.used_bin = n;
     }
-    const int max_num_cat = min(C.max_cat_threshold, (used_bin + 1) / 2);
-    for (int pass = 0; pass < 2; ++pass) {
+    __syncthreads();
+    used_bin = K.used_bin;
+    // stable rank sort by ctr ascending (ties: the earlier bin first, as std::stable_sort leaves them)
+    int my_bin = -1, rank = 0;
+    if (tid < used_bin) {
+      my_bin = K.sorted[tid];
+      const double mine = K.ctr[my_bin];
+      for (int j = 0; j < used_bin; ++j) {
+        const int bj = K.sorted[j];
+        const double cj = K.ctr[bj];
+        rank += (cj < mine || (cj == mine && j < tid)) ? 1 : 0;
+      }
+    }
+    __syncthreads();
+    if (tid < used_bin) K.tmp[rank] = (unsigned char)(bin_start + my_bin);   // data index t of the rank-th bin
+    __syncthreads();
+    if (tid < used_bin) K.sorted[tid] = K.tmp[tid];
+    K.cand_ok[tid] = 0;
+    __syncthreads();
+    const int max_num_cat = min(C.max_cat_threshold, (used_bin + 1) / 2);   // <= 128
+    if (tid == 0 || tid == 32) {   // one thread per direction: the accumulation and its tests, no gains
+      const int pass = tid == 0 ? 0 : 1;
       const int dir = pass == 0 ? 1 : -1;
       int start_pos = pass == 0 ? 0 : used_bin - 1;
       int cnt_cur_group = 0, left_count = 0;
       double lg = 0.0f, lh = LGB_EPS;
       for (int i = 0; i < used_bin && i < max_num_cat; ++i) {
-        const int t = sorted[start_pos];
+        const int tt = K.sorted[start_pos];
         start_pos += dir;
-        const double grad = G[t], hess = H[t];
+        const double grad = G[tt], hess = H[tt];
         const int cnt = round_int(hess * cnt_factor);
         lg += grad; lh += hess; left_count += cnt; cnt_cur_group += cnt;
         if (left_count < P.min_data_in_leaf || lh < P.min_sum_hessian) continue;
@@ -277,16 +302,33 @@ __device__ void cat_find_best_threshold(const double* __restrict__ G, const doub
         if (rh < P.min_sum_hessian) break;
         if (cnt_cur_group < C.min_data_per_group) continue;
         cnt_cur_group = 0;
-        const double rg = sum_g - lg;
-        const double gain = mc_split_gains(lg, lh, rg, rh, P, left_count, right_count, parent_output, M);
-        if (gain <= min_gain_shift) continue;
-        splittable = 1;
-        if (gain > best_gain) { best_lc = left_count; best_lg = lg; best_lh = lh; best_threshold = i; best_gain = gain; best_dir = dir; }
+        const int k = pass * 128 + i;
+        K.cand_g[k] = lg; K.cand_h[k] = lh; K.cand_c[k] = left_count; K.cand_ok[k] = 1;
       }
     }
+    __syncthreads();
+    if (K.cand_ok[tid]) {   // thread = direction * 128 + position: the reference's order of evaluation
+      c_lg = K.cand_g[tid]; c_lh = K.cand_h[tid]; c_lc = K.cand_c[tid];
+      gain = mc_split_gains(c_lg, c_lh, sum_g - c_lg, sum_h - c_lh, P, c_lc, num_data - c_lc, parent_output, M);
+      ok = gain > min_gain_shift;
+    }
   }
-  for (int w = 0; w < LGB_CAT_WORDS; ++w) bits[w] = 0u;
+  // block arg-max over the candidates that beat min_gain_shift: larger gain, then the smaller thread id
+  const int w = warp_argmax(gain, (unsigned)tid, 0u, ok);
+  if (lane == 0) { K.wpos[warp] = -1; K.wgain[warp] = LGB_MIN_SCORE; }
+  __syncwarp();
+  if (w >= 0 && lane == w) { K.wpos[warp] = tid; K.wgain[warp] = gain; }
+  __syncthreads();
+  int bp = -1; double bg = LGB_MIN_SCORE;
+#pragma unroll
+  for (int k = 0; k < FS_WARPS; ++k) if (K.wpos[k] >= 0 && (bp < 0 || K.wgain[k] > bg)) { bp = K.wpos[k]; bg = K.wgain[k]; }
+  // the winner publishes its sums (cand arrays double as the mailbox)
+  if (tid == bp) { K.cand_g[0] = c_lg; K.cand_h[0] = c_lh; K.cand_c[0] = c_lc; }
+  __syncthreads();
+  for (int wd = 0; wd < LGB_CAT_WORDS; ++wd) bits[wd] = 0u;
+  const int splittable = bp >= 0 ? 1 : 0;
   if (splittable) {
+    const double best_lg = K.cand_g[0], best_lh = K.cand_h[0]; const int best_lc = K.cand_c[0];
     o.left_output = mc_output(best_lg, best_lh, P, best_lc, parent_output, M);
     o.left_count = best_lc;
     o.left_sum_g = best_lg;
@@ -295,13 +337,14 @@ __device__ void cat_find_best_threshold(const double* __restrict__ G, const doub
     o.right_count = num_data - best_lc;
     o.right_sum_g = sum_g - best_lg;
     o.right_sum_h = sum_h - best_lh - LGB_EPS;
-    o.gain = best_gain - min_gain_shift;
+    o.gain = bg - min_gain_shift;
     if (use_onehot) {
-      const int b = best_threshold + offset;
+      const int b = bin_start + bp + offset;
       bits[b >> 5] |= 1u << (b & 31);
     } else {
+      const int best_dir = bp < 128 ? 1 : -1, best_threshold = bp & 127;
       for (int i = 0; i <= best_threshold; ++i) {
-        const int b = (best_dir == 1 ? sorted[i] : sorted[used_bin - 1 - i]) + offset;
+        const int b = (best_dir == 1 ? K.sorted[i] : K.sorted[used_bin - 1 - i]) + offset;
         bits[b >> 5] |= 1u << (b & 31);
       }
     }
@@ -309,6 +352,7 @@ __device__ void cat_find_best_threshold(const double* __restrict__ G, const doub
   o.gain *= F.penalty;
   *out = o;
   *splittable_out = splittable;
+  __syncthreads();
 }
 
 // The general counterpart of find_item: same inputs, same outputs, any number of bins, numerical or categorical.  All
@@ -324,10 +368,9 @@ __device__ void find_item_wide(const DevView& V, ScanSmem& S, int f, int sel, co
   HistEntry* ht = V.pool + (size_t)Lt.slot * V.total_bin + F.hist_base;   // scanned leaf (sel 1: holds the parent)
   __shared__ double s_fix[2];
   // the block scan's scratch lies over the 8-bit search's (unused on this path once the block sums above are done)
-  static_assert(sizeof(WideScratch) <= sizeof(ScanSmem), "WideScratch must fit ScanSmem");
+  static_assert(sizeof(WideScratch) + sizeof(CatScratch) + 16 <= sizeof(ScanSmem), "the general search's scratch must fit ScanSmem");
   WideScratch& s_scan = *reinterpret_cast<WideScratch*>(&S);
-  __shared__ unsigned char s_sorted[256];
-  __shared__ double s_ctr[256];
+  CatScratch& s_cat = *reinterpret_cast<CatScratch*>(reinterpret_cast<char*>(&S) + ((sizeof(WideScratch) + 15) & ~(size_t)15));
   DevSplit o; int sp = 0;
   o.gain = LGB_MIN_SCORE; o.feature = -1; o.real_feature = -1;
   if (used) {
@@ -389,17 +432,15 @@ __device__ void find_item_wide(const DevView& V, ScanSmem& S, int f, int sel, co
       if (F.cat) {
         for (int t = tid; t < nt; t += FS_THREADS) { s_scan.vg[t] = D.g(t); s_scan.vh[t] = D.hh(t); }   // nt <= 255 for a categorical feature
         __syncthreads();
-        if (tid == 0) {
-          unsigned bits[LGB_CAT_WORDS];
-          cat_find_best_threshold(s_scan.vg, s_scan.vh, F, V.p, V.cat, Lt.sum_g, Lt.sum_h, Lt.gcount, parent_output, M, s_sorted, s_ctr, bits, &o, &sp);
-          if (sp) {   // the set of bins going left takes the next pool entry; the split carries its index as "threshold"
-            const int e = atomicAdd(&c->cat_count, 1);
-            if (e < V.cat_cap) {
-              for (int w = 0; w < LGB_CAT_WORDS; ++w) V.cat_pool[(size_t)e * LGB_CAT_WORDS + w] = bits[w];
-              o.threshold = e;
-            } else {
-              c->cat_overflow = 1; o.gain = LGB_MIN_SCORE; sp = 0;
-            }
+        unsigned bits[LGB_CAT_WORDS];
+        cat_find_best_threshold_block(s_cat, s_scan.vg, s_scan.vh, F, V.p, V.cat, Lt.sum_g, Lt.sum_h, Lt.gcount, parent_output, M, bits, &o, &sp);
+        if (tid == 0 && sp) {   // the set of bins going left takes the next pool entry; the split carries its index as "threshold"
+          const int e = atomicAdd(&c->cat_count, 1);
+          if (e < V.cat_cap) {
+            for (int w = 0; w < LGB_CAT_WORDS; ++w) V.cat_pool[(size_t)e * LGB_CAT_WORDS + w] = bits[w];
+            o.threshold = e;
+          } else {
+            c->cat_overflow = 1; o.gain = LGB_MIN_SCORE; sp = 0;
           }
         }
       } else {
