@@ -48,7 +48,8 @@ enum { LGBCU_OBJ_NONE = 0, LGBCU_OBJ_BINARY = 1, LGBCU_OBJ_L2 = 2, LGBCU_OBJ_LAM
        LGBCU_OBJ_HUBER = 8 /* p0 = alpha */, LGBCU_OBJ_FAIR = 9 /* p0 = fair_c */, LGBCU_OBJ_POISSON = 10 /* p0 = poisson_max_delta_step */,
        LGBCU_OBJ_GAMMA = 11, LGBCU_OBJ_TWEEDIE = 12 /* p0 = tweedie_variance_power */,
        LGBCU_OBJ_XENTROPY = 13 /* cross_entropy: labels in [0, 1] */,
-       LGBCU_OBJ_MAPE = 14 /* L1 with the per-row weight 1 / max(1, |label|); no user weights */ };
+       LGBCU_OBJ_MAPE = 14 /* L1 with the per-row weight 1 / max(1, |label|); no user weights */,
+       LGBCU_OBJ_XENTLAMBDA = 15 /* cross_entropy_lambda */ };
 /* histogram kernel selection (LGBCU_HIST_AUTO picks by leaf size) */
 enum { LGBCU_HIST_AUTO = 0, LGBCU_HIST_GLOBAL_ATOMIC = 1, LGBCU_HIST_WARP_PRIVATE = 2 };
 
@@ -376,6 +377,7 @@ LGBCU_API int lgbcu_valid_copy_score(LgbCuContext* ctx, int32_t set, double* out
 #define LGBCU_METRIC_TWEEDIE 13        /* `sigmoid` = tweedie_variance_power */
 #define LGBCU_METRIC_BINARY_ERROR 14   /* `sigmoid` as for binary_logloss */
 #define LGBCU_METRIC_MAPE 16
+#define LGBCU_METRIC_XENTLAMBDA 17     /* cross_entropy_lambda: the weight sits inside the loss, the mean is over the rows */
 #define LGBCU_METRIC_XENTROPY 15       /* cross_entropy (labels in [0, 1]); `sigmoid` as for binary_logloss.  kullback_leibler is
                                         * this plus a constant of the labels, which the host adds */
 LGBCU_API int lgbcu_eval_set_ndcg(LgbCuContext* ctx, int32_t set, const int32_t* eval_at, int32_t num_eval,

@@ -60,6 +60,16 @@ __global__ void __launch_bounds__(EVAL_THREADS) k_eval_pointwise(int n, int kind
     } else if (kind == 9) {          // BinaryErrorMetric::LossOnPoint (binary_metric.hpp:143-149) of the converted score
       const double prob = sigmoid > 0.0 ? 1.0f / (1.0f + exp(-sigmoid * s)) : s;
       loss = prob <= 0.5f ? (y > 0 ? 1.0 : 0.0) : (y <= 0 ? 1.0 : 0.0);
+    } else if (kind == 12) {         // XentLambdaLoss (xentropy_metric.hpp:53-55) of hhat = log(1 + exp(score)); the weight is INSIDE
+      const double hhat = log(1.0f + exp(s));
+      const float w = weight ? weight[i] : 1.0f;
+      const double prob = 1.0f - exp(-w * hhat);
+      const double log_arg_epsilon = 1.0e-12;
+      double a = y, b = 1.0f - y;
+      a *= prob > log_arg_epsilon ? log(prob) : log(log_arg_epsilon);
+      b *= 1.0f - prob > log_arg_epsilon ? log(1.0f - prob) : log(log_arg_epsilon);
+      acc += -(a + b);
+      continue;
     } else if (kind == 11) {         // MAPEMetric::LossOnPoint (regression_metric.hpp:248-250)
       loss = fabs(y - s) / fmaxf(1.0f, fabsf(y));
     } else if (kind == 10) {         // XentLoss (xentropy_metric.hpp:34-50) of the converted score

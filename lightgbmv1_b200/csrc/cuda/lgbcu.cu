@@ -947,7 +947,7 @@ int lgbcu_set_query(LgbCuContext* c, const int32_t* boundaries, int32_t num_quer
 
 int lgbcu_set_objective(LgbCuContext* c, int kind, double p0, double p1, double p2) {
   NEED(c, "lgbcu: NULL context");
-  NEED(kind >= LGBCU_OBJ_NONE && kind <= LGBCU_OBJ_MAPE, "lgbcu_set_objective: unknown kind %d", kind);
+  NEED(kind >= LGBCU_OBJ_NONE && kind <= LGBCU_OBJ_XENTLAMBDA, "lgbcu_set_objective: unknown kind %d", kind);
   if (kind == LGBCU_OBJ_BINARY || kind == LGBCU_OBJ_LAMBDARANK) NEED(p0 > 0, "Sigmoid parameter %f should be greater than zero", p0);
   c->objective = kind; c->obj_p[0] = p0; c->obj_p[1] = p1; c->obj_p[2] = p2;
   c->rank_ready = false;
@@ -1020,7 +1020,8 @@ int lgbcu_get_gradients(LgbCuContext* c) {
              c->d_grad_base + off, c->d_hess_base + off, k);
     }
   } else if (c->objective == LGBCU_OBJ_HUBER || c->objective == LGBCU_OBJ_FAIR || c->objective == LGBCU_OBJ_POISSON ||
-             c->objective == LGBCU_OBJ_GAMMA || c->objective == LGBCU_OBJ_TWEEDIE || c->objective == LGBCU_OBJ_XENTROPY) {
+             c->objective == LGBCU_OBJ_GAMMA || c->objective == LGBCU_OBJ_TWEEDIE || c->objective == LGBCU_OBJ_XENTROPY ||
+             c->objective == LGBCU_OBJ_XENTLAMBDA) {
     LAUNCH(k_grad_regression, g, 256, 0, c->stream, c->N, c->objective, c->obj_p[0], c->d_score, c->d_label, w, c->d_grad, c->d_hess);
   } else if (c->objective == LGBCU_OBJ_L1) {
     LAUNCH(k_grad_l1, g, 256, 0, c->stream, c->N, c->d_score, c->d_label, w, c->d_grad, c->d_hess, 0);

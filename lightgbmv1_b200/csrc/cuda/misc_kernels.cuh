@@ -70,7 +70,22 @@ __global__ void k_grad_regression(int n, int kind, double p0, const double* __re
     } else if (kind == LGBCU_OBJ_TWEEDIE) { // RegressionTweedieLoss (:720-738); p0 = tweedie_variance_power
       g = -label[i] * exp((1 - p0) * score[i]) + exp((2 - p0) * score[i]);
       h = -label[i] * (1 - p0) * exp((1 - p0) * score[i]) + (2 - p0) * exp((2 - p0) * score[i]);
-    } else if (kind == LGBCU_OBJ_XENTROPY) { // CrossEntropy::GetGradients (xentropy_objective.hpp:77-96)
+    } else if (kind == LGBCU_OBJ_XENTLAMBDA && weight != nullptr) {   // CrossEntropyLambda::GetGradients, weighted (xentropy_objective.hpp:199-215)
+      const double w = weight[i];
+      const double y = label[i];
+      const double epf = exp(score[i]);
+      const double hhat = log(1.0f + epf);
+      const double z = 1.0f - exp(-w * hhat);
+      const double enf = 1.0f / epf;
+      grad[i] = (float)((1.0f - y / z) * w / (1.0f + enf));
+      const double c = 1.0f / (1.0f - z);
+      double d = 1.0f + epf;
+      const double a = w * epf / (d * d);
+      d = c - 1.0f;
+      const double b = (c / (d * d)) * (1.0f + w * epf - c);
+      hess[i] = (float)(a * (1.0f + y * b));
+      continue;
+    } else if (kind == LGBCU_OBJ_XENTROPY || kind == LGBCU_OBJ_XENTLAMBDA) { // CrossEntropy::GetGradients (the unweighted lambda form is the same) (xentropy_objective.hpp:77-96)
       const double z = 1.0f / (1.0f + exp(-score[i]));
       g = z - label[i];
       h = z * (1.0f - z);

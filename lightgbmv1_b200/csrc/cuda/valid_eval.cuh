@@ -238,7 +238,7 @@ int eval_auc(LgbCuContext* c, int n, const double* score, const float* label, co
 
 int lgbcu_eval(LgbCuContext* c, int32_t set, int32_t kind, double sigmoid, double* out, int32_t out_len) {
   NEED(c && out && out_len >= 1, "lgbcu_eval: bad argument");
-  NEED(kind >= LGBCU_METRIC_L2 && kind <= LGBCU_METRIC_MAPE, "lgbcu_eval: unknown metric kind %d", kind);
+  NEED(kind >= LGBCU_METRIC_L2 && kind <= LGBCU_METRIC_XENTLAMBDA, "lgbcu_eval: unknown metric kind %d", kind);
   USE_DEVICE(c->device);
   int n; const double* score; const float* label; const float* weight; const int* query; int nq; NdcgTables* nd;
   if (set < 0) {
@@ -290,7 +290,7 @@ int lgbcu_eval(LgbCuContext* c, int32_t set, int32_t kind, double sigmoid, doubl
   const int pk = kind == LGBCU_METRIC_BINARY_LOGLOSS ? 1 : kind == LGBCU_METRIC_L1 ? 2 : kind == LGBCU_METRIC_QUANTILE ? 3 :
                  kind == LGBCU_METRIC_HUBER ? 4 : kind == LGBCU_METRIC_FAIR ? 5 : kind == LGBCU_METRIC_POISSON ? 6 :
                  kind == LGBCU_METRIC_GAMMA ? 7 : kind == LGBCU_METRIC_TWEEDIE ? 8 : kind == LGBCU_METRIC_BINARY_ERROR ? 9 :
-                 kind == LGBCU_METRIC_XENTROPY ? 10 : kind == LGBCU_METRIC_MAPE ? 11 : 0;
+                 kind == LGBCU_METRIC_XENTROPY ? 10 : kind == LGBCU_METRIC_MAPE ? 11 : kind == LGBCU_METRIC_XENTLAMBDA ? 12 : 0;
   // metrics see the objective's ConvertOutput: exp for the log-link objectives
   const int conv_exp = (c->objective == LGBCU_OBJ_POISSON || c->objective == LGBCU_OBJ_GAMMA || c->objective == LGBCU_OBJ_TWEEDIE) ? 1 : 0;
   LAUNCH(k_eval_pointwise, grid, EVAL_THREADS, 0, c->stream, n, pk, sigmoid, conv_exp, score,
@@ -299,7 +299,8 @@ int lgbcu_eval(LgbCuContext* c, int32_t set, int32_t kind, double sigmoid, doubl
   CU(cudaGetLastError());
   CU(cudaMemcpyAsync(c->h_eval_out, c->d_eval_out, sizeof(double), cudaMemcpyDeviceToHost, c->stream));
   CU(cudaStreamSynchronize(c->stream));
-  const double avg = c->h_eval_out[0] / sum_w;
+  // (cross_entropy_lambda keeps the weight inside the loss and averages over the rows: xentropy_metric.hpp:224)
+  const double avg = c->h_eval_out[0] / (kind == LGBCU_METRIC_XENTLAMBDA ? (double)n : sum_w);
   out[0] = kind == LGBCU_METRIC_RMSE ? std::sqrt(avg) : avg;
   return 0;
 }

@@ -34,6 +34,7 @@ struct LoadedModel {
   std::string objective;   // the header's objective line, e.g. "binary sigmoid:1"
   double sigmoid = 0.0;    // > 0: predictions are 1 / (1 + exp(-sigmoid * raw))
   bool exp_out = false;    // the log-link regressions (poisson, gamma, tweedie): predictions are exp(raw)
+  bool softplus_out = false;   // cross_entropy_lambda: predictions are log(1 + exp(raw))
   int num_tree_per_iteration = 1;   // multiclass: trees (and outputs per row) per iteration
   bool softmax = false;             // "multiclass ...": predictions are the softmax of a row's raw scores
   double ova_sigmoid = 0.0;         // "multiclassova ...": > 0, a sigmoid per class
@@ -88,6 +89,7 @@ LoadedModel* ParseModel(const std::string& text) {
     if (p != std::string::npos) m->sigmoid = std::strtod(m->objective.c_str() + p + 8, nullptr);
   }
   if (m->objective.rfind("cross_entropy", 0) == 0 && m->objective.rfind("cross_entropy_lambda", 0) != 0) m->sigmoid = 1.0;
+  if (m->objective.rfind("cross_entropy_lambda", 0) == 0) m->softplus_out = true;
   if (m->objective.rfind("poisson", 0) == 0 || m->objective.rfind("gamma", 0) == 0 || m->objective.rfind("tweedie", 0) == 0) m->exp_out = true;
   // trees: "Tree=i" ... blank line, until "end of trees"
   std::string cur;
@@ -424,6 +426,7 @@ int LGBM_BoosterPredictForMat(BoosterHandle handle, const void* data, int data_t
         for (int t = 0; t < n_iter; ++t) for (int k = 0; k < K; ++k) sc[k] += m.trees[static_cast<size_t>(t) * K + k]->Predict(row.data());
         if (!raw && m.sigmoid > 0) sc[0] = 1.0f / (1.0f + std::exp(-m.sigmoid * sc[0]));
         if (!raw && m.exp_out) sc[0] = std::exp(sc[0]);
+        if (!raw && m.softplus_out) sc[0] = std::log(1.0f + std::exp(sc[0]));
         if (!raw && m.ova_sigmoid > 0) for (int k = 0; k < K; ++k) sc[k] = 1.0f / (1.0f + std::exp(-m.ova_sigmoid * sc[k]));
         if (!raw && m.softmax) {   // Common::Softmax
           double wmax = sc[0];

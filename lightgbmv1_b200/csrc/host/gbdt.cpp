@@ -148,10 +148,11 @@ GBDT::GBDT(const Dataset* train, const Config& config)
       spec.names = {config_.multi_error_top_k == 1 ? std::string("multi_error") : "multi_error@" + std::to_string(config_.multi_error_top_k)};
     }
     else if (m == "mape") { spec.kind = LGBCU_METRIC_MAPE; spec.names = {"mape"}; }
+    else if (m == "cross_entropy_lambda") { spec.kind = LGBCU_METRIC_XENTLAMBDA; spec.names = {"cross_entropy_lambda"}; }
     else if (m == "cross_entropy") { spec.kind = LGBCU_METRIC_XENTROPY; spec.names = {"cross_entropy"}; }
     else if (m == "kullback_leibler") { spec.kind = LGBCU_METRIC_XENTROPY; spec.names = {"kullback_leibler"}; spec.kl = true; }
     else if (m == "custom") continue;
-    else Log::Fatal("metric=%s is outside this library's path (l2, rmse, l1, huber, fair, poisson, gamma, tweedie, quantile, mape, binary_logloss, binary_error, cross_entropy, kullback_leibler, auc, ndcg, multi_logloss, multi_error)", m.c_str());
+    else Log::Fatal("metric=%s is outside this library's path (l2, rmse, l1, huber, fair, poisson, gamma, tweedie, quantile, mape, binary_logloss, binary_error, cross_entropy, cross_entropy_lambda, kullback_leibler, auc, ndcg, multi_logloss, multi_error)", m.c_str());
     if ((spec.kind == LGBCU_METRIC_MULTI_LOGLOSS || spec.kind == LGBCU_METRIC_MULTI_ERROR) != (num_tree_per_iteration_ > 1))
       Log::Fatal("Multiclass objective and metrics don't match");
     metrics_.push_back(spec);

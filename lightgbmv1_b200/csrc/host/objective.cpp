@@ -196,6 +196,43 @@ class RegressionPercentile : public Objective {
   data_size_t num_data_ = 0; const label_t* label_ = nullptr; const label_t* weights_ = nullptr;
 };
 
+// src/objective/xentropy_objective.hpp:150-283 (CrossEntropyLambda): labels in [0, 1], weights inside the link
+class CrossEntropyLambda : public Objective {
+ public:
+  explicit CrossEntropyLambda(const Config&) {}
+  void Init(const Metadata& meta, data_size_t n, const SumSync&) override {
+    num_data_ = n; label_ = meta.label.data(); weights_ = meta.weights.empty() ? nullptr : meta.weights.data();
+    if (meta.label.empty()) Log::Fatal("Label should not be NULL");
+    for (data_size_t i = 0; i < n; ++i)
+      if (!(label_[i] >= 0.0f && label_[i] <= 1.0f)) Log::Fatal("[%s]: does not tolerate element [#%d = %f] outside [0, 1]", Name(), i, label_[i]);
+    if (weights_) {
+      label_t minw = weights_[0];
+      for (data_size_t i = 0; i < n; ++i) minw = std::min(minw, weights_[i]);
+      if (minw <= 0.0f) Log::Fatal("[%s]: at least one weight is non-positive", Name());
+    }
+  }
+  void Configure(LgbCuContext* ctx) const override { Check(lgbcu_set_objective(ctx, LGBCU_OBJ_XENTLAMBDA, 0, 0, 0)); }
+  double BoostFromScore(int) const override {
+    double suml = 0.0f, sumw = 0.0f;
+    if (weights_) {
+#pragma omp parallel for schedule(static) reduction(+:suml, sumw)
+      for (data_size_t i = 0; i < num_data_; ++i) { suml += label_[i] * weights_[i]; sumw += weights_[i]; }
+    } else {
+      sumw = static_cast<double>(num_data_);
+#pragma omp parallel for schedule(static) reduction(+:suml)
+      for (data_size_t i = 0; i < num_data_; ++i) suml += label_[i];
+    }
+    const double havg = suml / sumw;
+    return std::log(std::exp(havg) - 1.0f);
+  }
+  void ConvertOutput(const double* in, double* out) const override { out[0] = std::log(1.0f + std::exp(in[0])); }
+  std::string ToString() const override { return Name(); }
+  const char* Name() const override { return "cross_entropy_lambda"; }
+
+ private:
+  data_size_t num_data_ = 0; const label_t* label_ = nullptr; const label_t* weights_ = nullptr;
+};
+
 // RegressionMAPELOSS (src/objective/regression_objective.hpp:577-669): L1 with label_weight_ = 1 / max(1, |label|)
 class RegressionMAPE : public Objective {
  public:
@@ -408,6 +445,7 @@ Objective* Objective::Create(const Config& c) {
   if (c.objective == "regression_l1") return new RegressionPercentile(c, false);
   if (c.objective == "quantile") return new RegressionPercentile(c, true);
   if (c.objective == "cross_entropy") return new CrossEntropy(c);
+  if (c.objective == "cross_entropy_lambda") return new CrossEntropyLambda(c);
   if (c.objective == "mape") return new RegressionMAPE(c);
   if (c.objective == "binary") return new BinaryLogloss(c);
   if (c.objective == "regression") return new RegressionL2(c);

@@ -196,7 +196,7 @@ def test_errors_surface_through_last_error():
     ds = ours.dataset_from_mat(X, "verbosity=-1")
     ours.set_field(ds, "label", y)
     with pytest.raises(capi.LGBMError):
-        ours.booster_create(ds, "objective=cross_entropy_lambda")
+        ours.booster_create(ds, "objective=rank_xendcg")
     with pytest.raises(capi.LGBMError):
         ours.booster_create(ds, "objective=binary boosting=dart")
     with pytest.raises(capi.LGBMError):

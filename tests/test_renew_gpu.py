@@ -106,3 +106,26 @@ def test_cross_entropy_identical_trees(weighted, metric):
     loaded = ref.load_model_from_string(ours.model_string(bo))
     Xt, _ = make(3000, 33)
     np.testing.assert_allclose(ours.predict_mat(bo, Xt), ref.predict_mat(loaded, Xt), rtol=0, atol=1e-12)
+
+
+@pytest.mark.parametrize("weighted", [False, True])
+def test_cross_entropy_lambda_identical_trees(weighted):
+    """CrossEntropyLambda (xentropy_objective.hpp:150-283): the weights sit inside the link (a separate gradient form when
+    weights are given); its metric keeps them inside the loss and averages over the rows."""
+    X, _ = make(40_000, 41)
+    rng = np.random.default_rng(42)
+    p = 1.0 / (1.0 + np.exp(-(1.2 * X[:, 0] - X[:, 1] * X[:, 2] + 0.3 * rng.standard_normal(len(X)))))
+    y = np.where(rng.random(len(X)) < 0.3, (rng.random(len(X)) < p).astype(np.float64), p).astype(np.float32)
+    w = (rng.random(len(y)).astype(np.float32) * 1.5 + 0.5) if weighted else None
+    params = "objective=cross_entropy_lambda num_leaves=31 learning_rate=0.1 min_data_in_leaf=20 verbosity=-1 num_threads=4"
+    ref, ours, br, bo, nr, no = run_both(X, y, params, 10, weight=w)
+    assert nr == no == 10
+    assert_same_model(ref, ours, br, bo)
+    np.testing.assert_allclose(ours.get_predict(bo, len(y)), ref.get_predict(br, len(y)), rtol=1e-9, atol=1e-12)
+    assert ours.eval_names(bo) == ref.eval_names(br) == ["cross_entropy_lambda"]
+    np.testing.assert_allclose(ours.get_eval(bo, 0), ref.get_eval(br, 0), rtol=1e-9)
+    loaded = ref.load_model_from_string(ours.model_string(bo))
+    Xt, _ = make(3000, 43)
+    np.testing.assert_allclose(ours.predict_mat(bo, Xt), ref.predict_mat(loaded, Xt), rtol=0, atol=1e-12)
+    mine = ours.load_model_from_string(ref.model_string(br))
+    np.testing.assert_allclose(ours.predict_mat(mine, Xt), ref.predict_mat(br, Xt), rtol=0, atol=1e-12)
