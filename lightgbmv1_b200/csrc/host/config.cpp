@@ -45,6 +45,7 @@ const std::unordered_map<std::string, std::string>& Aliases() {
       {"mc", "monotone_constraints"}, {"monotone_constraint", "monotone_constraints"},
       {"monotone_constraining_method", "monotone_constraints_method"}, {"mc_method", "monotone_constraints_method"},
       {"monotone_splits_penalty", "monotone_penalty"}, {"ms_penalty", "monotone_penalty"}, {"mc_penalty", "monotone_penalty"},
+      {"rate_drop", "drop_rate"},
       {"cat_feature", "categorical_feature"}, {"categorical_column", "categorical_feature"}, {"cat_column", "categorical_feature"},
   };
   return t;
@@ -159,7 +160,7 @@ void Config::Set(const std::unordered_map<std::string, std::string>& p) {
     const int int_max = std::numeric_limits<int16_t>::max();
     data_random_seed = rand.NextShort(0, int_max);
     bagging_seed = rand.NextShort(0, int_max);
-    (void)rand.NextShort(0, int_max);  // drop_seed
+    drop_seed = rand.NextShort(0, int_max);
     feature_fraction_seed = rand.NextShort(0, int_max);
     objective_seed = rand.NextShort(0, int_max);
     (void)rand.NextShort(0, int_max);  // extra_seed
@@ -169,7 +170,8 @@ void Config::Set(const std::unordered_map<std::string, std::string>& p) {
     std::transform(s.begin(), s.end(), s.begin(), ::tolower);
     if (s == "gbdt" || s == "gbrt") boosting = "gbdt";
     else if (s == "goss") boosting = "goss";
-    else Log::Fatal("boosting=%s is outside this library's path (gbdt and goss are built)", s.c_str());
+    else if (s == "dart") boosting = "dart";
+    else Log::Fatal("boosting=%s is outside this library's path (gbdt, goss and dart are built)", s.c_str());
   }
   if (GetStr(p, "objective", &s)) objective = ObjectiveAlias(s);
   // GetMetricType (src/io/config.cpp:87-100): lower-case, split on ',', ParseMetricAlias, drop repeats; with no
@@ -263,6 +265,14 @@ void Config::Set(const std::unordered_map<std::string, std::string>& p) {
       categorical_feature.push_back(static_cast<int>(v));
     }
   }
+  GetDouble(p, "drop_rate", &drop_rate);
+  GetDouble(p, "skip_drop", &skip_drop);
+  GetInt(p, "max_drop", &max_drop);
+  GetInt(p, "drop_seed", &drop_seed);
+  GetBool(p, "xgboost_dart_mode", &xgboost_dart_mode);
+  GetBool(p, "uniform_drop", &uniform_drop);
+  if (drop_rate < 0.0 || drop_rate > 1.0) Log::Fatal("drop_rate should be in [0, 1]");
+  if (skip_drop < 0.0 || skip_drop > 1.0) Log::Fatal("skip_drop should be in [0, 1]");
   GetInt(p, "min_data_per_group", &min_data_per_group);
   GetInt(p, "max_cat_threshold", &max_cat_threshold);
   GetInt(p, "max_cat_to_onehot", &max_cat_to_onehot);

@@ -39,6 +39,8 @@ GBDT::GBDT(const Dataset* train, const Config& config)
       feature_rand_(config.feature_fraction_seed) {
   const int N = train_->num_data(), F = train_->num_features();
   if (F <= 0) Log::Fatal("the CUDA learner needs at least one non-constant feature");
+  is_dart_ = config_.boosting == "dart";
+  random_for_drop_ = Random(config_.drop_seed);
   StageTimer st;
   objective_.reset(Objective::Create(config_));
   // ---- device learner (TreeLearner::Init + ScoreUpdater ctor, gbdt.cpp:78-91)
@@ -318,8 +320,10 @@ bool GBDT::TrainOneIter(const float* grad, const float* hess) {
       }
     }
     st.tick("boost from average");
+    if (is_dart_) DroppingTrees();   // DART::GetTrainingScore: the gradients are taken without the dropped trees
     Check(lgbcu_get_gradients(ctx_));  // GBDT::Boosting: every class's gradients from the scores as they are now
   } else {
+    if (is_dart_) Log::Fatal("boosting=dart with gradients from the caller is outside this library's path");
     for (int k = 0; k < K; ++k) {
       Check(lgbcu_set_class(ctx_, k));
       Check(lgbcu_set_gradients(ctx_, grad + static_cast<size_t>(k) * N, hess + static_cast<size_t>(k) * N, N));
@@ -423,7 +427,90 @@ bool GBDT::TrainOneIter(const float* grad, const float* hess) {
     return true;
   }
   ++iter_;
+  if (is_dart_) {   // DART::TrainOneIter after GBDT::TrainOneIter
+    Normalize();
+    if (!config_.uniform_drop) { tree_weight_.push_back(shrinkage_rate_); sum_weight_ += shrinkage_rate_; }
+  }
   return false;
+}
+
+// ---- boosting=dart (src/boosting/dart.hpp) -------------------------------------------------------------------------
+
+void GBDT::AddTreeToTrain(const Tree& t, int class_id) {
+  Check(lgbcu_set_class(ctx_, class_id));
+  if (t.num_cat() > 0) Check(lgbcu_set_tree_cat_sets(ctx_, t.cat_bin_sets().data(), t.num_cat()));
+  std::vector<int> thr(t.threshold_in_bin().begin(), t.threshold_in_bin().end());
+  Check(lgbcu_add_score_by_tree(ctx_, t.num_leaves(), t.split_feature_inner().data(), thr.data(), t.decision_type().data(),
+                                t.left_child().data(), t.right_child().data(), t.leaf_values().data(), nullptr, 0, 0));
+}
+
+// DART::DroppingTrees (dart.hpp:87-142)
+void GBDT::DroppingTrees() {
+  const int K = num_tree_per_iteration_;
+  drop_index_.clear();
+  const bool is_skip = random_for_drop_.NextFloat() < config_.skip_drop;
+  if (!is_skip) {
+    double drop_rate = config_.drop_rate;
+    if (!config_.uniform_drop) {
+      const double inv_average_weight = static_cast<double>(tree_weight_.size()) / sum_weight_;
+      if (config_.max_drop > 0) drop_rate = std::min(drop_rate, config_.max_drop * inv_average_weight / sum_weight_);
+      for (int i = 0; i < iter_; ++i) {
+        if (random_for_drop_.NextFloat() < drop_rate * tree_weight_[i] * inv_average_weight) {
+          drop_index_.push_back(i);
+          if (drop_index_.size() >= static_cast<size_t>(config_.max_drop)) break;
+        }
+      }
+    } else {
+      if (config_.max_drop > 0) drop_rate = std::min(drop_rate, config_.max_drop / static_cast<double>(iter_));
+      for (int i = 0; i < iter_; ++i) {
+        if (random_for_drop_.NextFloat() < drop_rate) {
+          drop_index_.push_back(i);
+          if (drop_index_.size() >= static_cast<size_t>(config_.max_drop)) break;
+        }
+      }
+    }
+  }
+  for (int i : drop_index_) {
+    for (int k = 0; k < K; ++k) {
+      Tree& t = *models_[static_cast<size_t>(i) * K + k];
+      t.Shrinkage(-1.0);
+      AddTreeToTrain(t, k);
+    }
+  }
+  Check(lgbcu_set_class(ctx_, 0));
+  if (!config_.xgboost_dart_mode) {
+    shrinkage_rate_ = config_.learning_rate / (1.0f + static_cast<double>(drop_index_.size()));
+  } else {
+    if (drop_index_.empty()) shrinkage_rate_ = config_.learning_rate;
+    else shrinkage_rate_ = config_.learning_rate / (config_.learning_rate + static_cast<double>(drop_index_.size()));
+  }
+}
+
+// DART::Normalize (dart.hpp:144-196)
+void GBDT::Normalize() {
+  const int K = num_tree_per_iteration_;
+  const double k = static_cast<double>(drop_index_.size());
+  for (int i : drop_index_) {
+    for (int c = 0; c < K; ++c) {
+      Tree& t = *models_[static_cast<size_t>(i) * K + c];
+      // the tree is at -1 x itself: first its share leaves the validation scores, then it returns to the training scores
+      t.Shrinkage(!config_.xgboost_dart_mode ? 1.0f / (k + 1.0f) : shrinkage_rate_);
+      Check(lgbcu_set_class(ctx_, c));
+      AddTreeToValid(t);
+      t.Shrinkage(!config_.xgboost_dart_mode ? -k : -k / config_.learning_rate);
+      AddTreeToTrain(t, c);
+    }
+    if (!config_.uniform_drop) {
+      if (!config_.xgboost_dart_mode) {
+        sum_weight_ -= tree_weight_[i] * (1.0f / (k + 1.0f));
+        tree_weight_[i] *= (k / (k + 1.0f));
+      } else {
+        sum_weight_ -= tree_weight_[i] * (1.0f / (k + config_.learning_rate));
+        tree_weight_[i] *= (k / (k + config_.learning_rate));
+      }
+    }
+  }
+  Check(lgbcu_set_class(ctx_, 0));
 }
 
 void GBDT::GetTrainScore(double* out, bool converted) const {
@@ -444,6 +531,7 @@ void GBDT::GetTrainScore(double* out, bool converted) const {
 
 void GBDT::AddTreeToValid(const Tree& tree) {
   if (valid_.empty()) return;
+  if (tree.num_cat() > 0) Check(lgbcu_set_tree_cat_sets(ctx_, tree.cat_bin_sets().data(), tree.num_cat()));
   std::vector<int> thr(tree.threshold_in_bin().begin(), tree.threshold_in_bin().end());
   for (const ValidEntry& v : valid_) {
     Check(lgbcu_valid_add_tree(ctx_, v.set, tree.num_leaves(), tree.split_feature_inner().data(), thr.data(),

@@ -65,6 +65,15 @@ class GBDT {
   struct ValidEntry { const Dataset* data; int set; };
   void SetupNdcg(int set, const Metadata& md, int num_data);
   void AddTreeToValid(const Tree& tree);
+  // boosting=dart (src/boosting/dart.hpp:20-205): trees dropped before the gradients are taken, put back scaled after
+  bool is_dart_ = false;
+  Random random_for_drop_;
+  std::vector<double> tree_weight_;
+  double sum_weight_ = 0.0;
+  std::vector<int> drop_index_;
+  void DroppingTrees();
+  void Normalize();
+  void AddTreeToTrain(const Tree& tree, int class_id);   // ScoreUpdater::AddScore(tree, class) over every training row
   bool has_categorical_ = false;   // some feature of the training data is categorical
   std::vector<MetricSpec> metrics_;
   std::vector<int> eval_at_;
