@@ -338,6 +338,9 @@ LGBCU_API int lgbcu_valid_set_weight(LgbCuContext* ctx, int32_t set, const float
 LGBCU_API int lgbcu_valid_set_query(LgbCuContext* ctx, int32_t set, const int32_t* boundaries, int32_t num_queries);
 LGBCU_API int lgbcu_valid_set_score(LgbCuContext* ctx, int32_t set, const double* score, int32_t n);
 LGBCU_API int lgbcu_valid_add_const(LgbCuContext* ctx, int32_t set, double value);
+/* ScoreUpdater::MultiplyScore (score_updater.hpp:84-91) of the current class's scores: training data / a validation set */
+LGBCU_API int lgbcu_multiply_score(LgbCuContext* ctx, double value);
+LGBCU_API int lgbcu_valid_multiply_score(LgbCuContext* ctx, int32_t set, double value);
 LGBCU_API int lgbcu_valid_add_tree(LgbCuContext* ctx, int32_t set, int32_t num_leaves, const int32_t* split_feature_inner,
                                    const int32_t* threshold_bin, const int8_t* decision_type, const int32_t* left_child,
                                    const int32_t* right_child, const double* leaf_value);

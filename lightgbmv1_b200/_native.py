@@ -65,7 +65,7 @@ HIST_AUTO, HIST_GLOBAL_ATOMIC, HIST_WARP_PRIVATE = 0, 1, 2
 
 # every symbol include/lgbcu.h declares (tests check that the library exports all of them)
 LGBCU_SYMBOLS = [
-    "lgbcu_last_error", "lgbcu_set_cat_params", "lgbcu_set_monotone", "lgbcu_tree_cat_sets", "lgbcu_set_tree_cat_sets", "lgbcu_device_count", "lgbcu_launch_count", "lgbcu_create", "lgbcu_destroy",
+    "lgbcu_last_error", "lgbcu_multiply_score", "lgbcu_valid_multiply_score", "lgbcu_set_cat_params", "lgbcu_set_monotone", "lgbcu_tree_cat_sets", "lgbcu_set_tree_cat_sets", "lgbcu_device_count", "lgbcu_launch_count", "lgbcu_create", "lgbcu_destroy",
     "lgbcu_synchronize", "lgbcu_set_dataset", "lgbcu_set_dataset_columns", "lgbcu_set_tree_params",
     "lgbcu_set_hist_mode", "lgbcu_set_label", "lgbcu_set_weight", "lgbcu_set_query", "lgbcu_set_objective",
     "lgbcu_set_label_gain", "lgbcu_get_gradients", "lgbcu_set_gradients", "lgbcu_copy_gradients",

@@ -1079,6 +1079,15 @@ int lgbcu_add_score_const(LgbCuContext* c, double val) {
   return 0;
 }
 
+// ScoreUpdater::MultiplyScore of the current class's training scores (boosting=rf keeps the scores as running means)
+int lgbcu_multiply_score(LgbCuContext* c, double val) {
+  NEED(c && c->N > 0, "lgbcu_multiply_score: dataset not set");
+  USE_DEVICE(c->device);
+  LAUNCH(k_mul_const, grid_for(c, c->N, 256), 256, 0, c->stream, c->N, c->d_score, val);
+  CU(cudaGetLastError());
+  return 0;
+}
+
 int lgbcu_copy_score(LgbCuContext* c, double* score, int32_t n) {
   NEED(c && score && n == c->N, "lgbcu_copy_score: bad argument");
   USE_DEVICE(c->device);

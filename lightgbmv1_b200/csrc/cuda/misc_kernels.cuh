@@ -337,6 +337,11 @@ __global__ void k_add_const(int n, double* score, double v) {
   for (int i = blockIdx.x * blockDim.x + threadIdx.x; i < n; i += gridDim.x * blockDim.x) score[i] += v;
 }
 
+// ScoreUpdater::MultiplyScore (score_updater.hpp:84-91)
+__global__ void k_mul_const(int n, double* score, double v) {
+  for (int i = blockIdx.x * blockDim.x + threadIdx.x; i < n; i += gridDim.x * blockDim.x) score[i] *= v;
+}
+
 // packed [n][F] rows -> padded [n][row_stride] rows (one thread per 4 output bytes)
 __global__ void k_pad_rows(long long n, int F, int row_stride, const uint8_t* __restrict__ src, uint8_t* __restrict__ dst) {
   const long long words = n * (row_stride / 4);

@@ -119,6 +119,14 @@ int lgbcu_valid_add_const(LgbCuContext* c, int32_t set, double value) {
   return 0;
 }
 
+int lgbcu_valid_multiply_score(LgbCuContext* c, int32_t set, double value) {
+  ValidSet* v; if (valid_get(c, set, &v)) return -1;
+  USE_DEVICE(c->device);
+  LAUNCH(k_mul_const, grid_for(c, v->n, 256), 256, 0, c->stream, v->n, v->d_score, value);
+  CU(cudaGetLastError());
+  return 0;
+}
+
 int lgbcu_valid_add_tree(LgbCuContext* c, int32_t set, int32_t num_leaves, const int32_t* split_feature_inner,
                          const int32_t* threshold_bin, const int8_t* decision_type, const int32_t* left_child,
                          const int32_t* right_child, const double* leaf_value) {

@@ -35,6 +35,7 @@ struct LoadedModel {
   double sigmoid = 0.0;    // > 0: predictions are 1 / (1 + exp(-sigmoid * raw))
   bool exp_out = false;    // the log-link regressions (poisson, gamma, tweedie): predictions are exp(raw)
   bool softplus_out = false;   // cross_entropy_lambda: predictions are log(1 + exp(raw))
+  bool average_output = false; // boosting=rf: the header's "average_output" line
   int num_tree_per_iteration = 1;   // multiclass: trees (and outputs per row) per iteration
   bool softmax = false;             // "multiclass ...": predictions are the softmax of a row's raw scores
   double ova_sigmoid = 0.0;         // "multiclassova ...": > 0, a sigmoid per class
@@ -69,7 +70,7 @@ LoadedModel* ParseModel(const std::string& text) {
   while (in_header && next_line(&line)) {
     if (line.rfind("Tree=", 0) == 0) { pos -= line.size() + 1; break; }
     const size_t eq = line.find('=');
-    if (eq == std::string::npos) continue;
+    if (eq == std::string::npos) { if (line == "average_output") m->average_output = true; continue; }
     const std::string k = line.substr(0, eq), v = line.substr(eq + 1);
     if (k == "max_feature_idx") m->max_feature_idx = std::atoi(v.c_str());
     else if (k == "objective") m->objective = v;
@@ -424,6 +425,7 @@ int LGBM_BoosterPredictForMat(BoosterHandle handle, const void* data, int data_t
         }
         for (int k = 0; k < K; ++k) sc[k] = 0.0;
         for (int t = 0; t < n_iter; ++t) for (int k = 0; k < K; ++k) sc[k] += m.trees[static_cast<size_t>(t) * K + k]->Predict(row.data());
+        if (!raw && m.average_output && n_iter > 0) for (int k = 0; k < K; ++k) sc[k] /= n_iter;
         if (!raw && m.sigmoid > 0) sc[0] = 1.0f / (1.0f + std::exp(-m.sigmoid * sc[0]));
         if (!raw && m.exp_out) sc[0] = std::exp(sc[0]);
         if (!raw && m.softplus_out) sc[0] = std::log(1.0f + std::exp(sc[0]));

@@ -171,7 +171,8 @@ void Config::Set(const std::unordered_map<std::string, std::string>& p) {
     if (s == "gbdt" || s == "gbrt") boosting = "gbdt";
     else if (s == "goss") boosting = "goss";
     else if (s == "dart") boosting = "dart";
-    else Log::Fatal("boosting=%s is outside this library's path (gbdt, goss and dart are built)", s.c_str());
+    else if (s == "rf" || s == "random_forest") boosting = "rf";
+    else Log::Fatal("boosting=%s is outside this library's path (gbdt, goss, dart and rf are built)", s.c_str());
   }
   if (GetStr(p, "objective", &s)) objective = ObjectiveAlias(s);
   // GetMetricType (src/io/config.cpp:87-100): lower-case, split on ',', ParseMetricAlias, drop repeats; with no

@@ -205,6 +205,8 @@ GBDT::GBDT(const Dataset* train, const Config& config)
     used_cnt_bytree_ = std::max(RoundInt(total * config_.feature_fraction), std::min(1, total));
   }
   ResetFeatureMask();
+  is_rf_ = config_.boosting == "rf";
+  if (is_rf_) RFInit();
 }
 
 GBDT::~GBDT() {
@@ -295,7 +297,129 @@ void GBDT::GossSample(int iter) {
   bag_cnt_ = cnt;
 }
 
+// The device's split records -> Tree::Split / Tree::SplitCategorical, in order: node numbering, leaf ids and the model
+// text come out as the reference's (SerialTreeLearner::SplitInner, serial_tree_learner.cpp:541-659)
+void GBDT::ReplayRecords(Tree* tree, int ns) {
+  std::vector<uint32_t> cat_sets;   // the tree's categorical bin sets (8 words each), if it has any
+  if (has_categorical_) {
+    int32_t nsets = 0;
+    Check(lgbcu_tree_cat_sets(ctx_, nullptr, 0, &nsets));
+    if (nsets > 0) { cat_sets.resize(static_cast<size_t>(nsets) * 8); Check(lgbcu_tree_cat_sets(ctx_, cat_sets.data(), nsets, &nsets)); }
+  }
+  for (int i = 0; i < ns; ++i) {
+    const LgbCuSplitRecord& r = records_[i];
+    const BinMapper& m = train_->mapper(r.feature);
+    if (m.is_categorical()) {
+      // SerialTreeLearner::SplitInner, categorical branch (serial_tree_learner.cpp:592-621): the record names its set
+      // of bins; the model carries the set of the bins' category values
+      if (r.threshold < 0 || static_cast<size_t>(r.threshold) * 8 + 8 > cat_sets.size()) Log::Fatal("categorical split names bin set %d of %d", r.threshold, static_cast<int>(cat_sets.size() / 8));
+      const uint32_t* bin_set = cat_sets.data() + static_cast<size_t>(r.threshold) * 8;
+      std::vector<uint32_t> cat_set;   // Common::ConstructBitset over RealThreshold(bin)
+      for (int b = 0; b < m.num_bin(); ++b) {
+        if (!((bin_set[b >> 5] >> (b & 31)) & 1u)) continue;
+        const int v = static_cast<int>(m.BinToValue(b));
+        const int i1 = v / 32, i2 = v % 32;
+        if (static_cast<int>(cat_set.size()) < i1 + 1) cat_set.resize(i1 + 1, 0);
+        cat_set[i1] |= (1u << i2);
+      }
+      tree->SplitCategorical(r.leaf, r.feature, r.real_feature, bin_set, cat_set, r.left_output, r.right_output, r.left_count,
+                             r.right_count, r.left_sum_hessian, r.right_sum_hessian, r.gain, m.missing_type());
+      continue;
+    }
+    tree->Split(r.leaf, r.feature, r.real_feature, static_cast<uint32_t>(r.threshold), m.BinToValue(r.threshold),
+                r.left_output, r.right_output, r.left_count, r.right_count, r.left_sum_hessian, r.right_sum_hessian,
+                r.gain, m.missing_type(), r.default_left != 0);
+  }
+
+}
+
+// ---- boosting=rf (src/boosting/rf.hpp) -----------------------------------------------------------------------------
+
+void GBDT::MultiplyScore(int class_id, double val) {   // RF::MultiplyScore: training and validation scores
+  Check(lgbcu_set_class(ctx_, class_id));
+  Check(lgbcu_multiply_score(ctx_, val));
+  for (const ValidEntry& v : valid_) Check(lgbcu_valid_multiply_score(ctx_, v.set, val));
+}
+
+// RF::Init + RF::Boosting (rf.hpp:34-53, 79-99)
+void GBDT::RFInit() {
+  if (!(config_.bagging_freq > 0 && config_.bagging_fraction < 1.0 && config_.bagging_fraction > 0.0))
+    Log::Fatal("Check failed: config->bagging_freq > 0 && config->bagging_fraction < 1.0f && config->bagging_fraction > 0.0f");
+  if (!(config_.feature_fraction <= 1.0 && config_.feature_fraction > 0.0)) Log::Fatal("Check failed: config->feature_fraction <= 1.0f && config->feature_fraction > 0.0f");
+  if (has_init_score_) Log::Fatal("Check failed: (train_data->metadata().init_score()) == (nullptr)");
+  if (!objective_) Log::Fatal("RF mode do not support custom objective function, please use built-in objectives.");
+  if (objective_->IsRenewTreeOutput()) Log::Fatal("boosting=rf with a leaf-renewing objective (regression_l1, quantile, mape) is outside this library's path");
+  if (is_goss_) Log::Fatal("boosting=rf cannot be combined with goss");
+  shrinkage_rate_ = 1.0f;
+  const int K = num_tree_per_iteration_;
+  rf_init_scores_.assign(K, 0.0);
+  for (int k = 0; k < K; ++k) {   // BoostFromAverage(k, false)
+    if (!config_.boost_from_average) continue;
+    double s = objective_->BoostFromScore(k);
+    if (data_parallel_) { Check(lgbcu_comm_allreduce_sum_f64(ctx_, &s, 1)); s /= Net().num_machines; }
+    if (std::fabs(s) > kEpsilon) { rf_init_scores_[k] = s; Log::Info("Start training from score %lf", s); }
+  }
+  // the gradients of every iteration: the objective at the constant initial scores (the scores themselves stay 0: the
+  // constants are added, the gradients taken, the constants subtracted -- 0 + x - x is exact)
+  for (int k = 0; k < K; ++k) if (rf_init_scores_[k] != 0.0) { Check(lgbcu_set_class(ctx_, k)); Check(lgbcu_add_score_const(ctx_, rf_init_scores_[k])); }
+  Check(lgbcu_set_class(ctx_, 0));
+  Check(lgbcu_get_gradients(ctx_));
+  for (int k = 0; k < K; ++k) if (rf_init_scores_[k] != 0.0) { Check(lgbcu_set_class(ctx_, k)); Check(lgbcu_add_score_const(ctx_, -rf_init_scores_[k])); }
+  Check(lgbcu_set_class(ctx_, 0));
+}
+
+// RF::TrainOneIter (rf.hpp:101-159)
+bool GBDT::RFTrainOneIter() {
+  const int N = train_->num_data();
+  const int K = num_tree_per_iteration_;
+  Bagging(iter_);
+  const bool bagged = use_bagging_ && bag_cnt_ < N;
+  for (int k = 0; k < K; ++k) {
+    Check(lgbcu_set_class(ctx_, k));
+    std::unique_ptr<Tree> tree(new Tree(2));
+    if (class_need_train_[k]) {
+      ResetFeatureMask();
+      Check(lgbcu_begin_tree(ctx_, bagged ? LGBCU_DEVICE_BAG : nullptr, bagged ? bag_cnt_ : 0, need_reset_bytree_ ? feature_used_.data() : nullptr));
+      int ns = 0;
+      Check(lgbcu_train_tree(ctx_, records_.data(), &ns));
+      tree.reset(new Tree(config_.num_leaves));
+      ReplayRecords(tree.get(), ns);
+    }
+    if (tree->num_leaves() > 1) {
+      if (std::fabs(rf_init_scores_[k]) > kEpsilon) tree->AddBias(rf_init_scores_[k]);
+      MultiplyScore(k, static_cast<double>(iter_));
+      Check(lgbcu_set_class(ctx_, k));
+      Check(lgbcu_add_score_by_partition(ctx_, tree->leaf_values().data(), tree->num_leaves()));
+      if (tree->num_cat() > 0 && (bagged || !valid_.empty())) Check(lgbcu_set_tree_cat_sets(ctx_, tree->cat_bin_sets().data(), tree->num_cat()));
+      if (bagged) {
+        std::vector<int> thr(tree->threshold_in_bin().begin(), tree->threshold_in_bin().end());
+        Check(lgbcu_add_score_by_tree(ctx_, tree->num_leaves(), tree->split_feature_inner().data(), thr.data(), tree->decision_type().data(),
+                                      tree->left_child().data(), tree->right_child().data(), tree->leaf_values().data(), LGBCU_DEVICE_OOB, N - bag_cnt_, 0));
+      }
+      AddTreeToValid(*tree);
+      MultiplyScore(k, 1.0 / (iter_ + 1));
+    } else if (models_.size() < static_cast<size_t>(K)) {
+      double output = 0.0;
+      if (!class_need_train_[k]) output = objective_->BoostFromScore(k);
+      tree->AsConstantTree(output);
+      MultiplyScore(k, static_cast<double>(iter_));
+      Check(lgbcu_set_class(ctx_, k));
+      Check(lgbcu_add_score_const(ctx_, output));
+      for (const ValidEntry& v : valid_) Check(lgbcu_valid_add_const(ctx_, v.set, output));
+      MultiplyScore(k, 1.0 / (iter_ + 1));
+    }
+    models_.push_back(std::move(tree));
+  }
+  Check(lgbcu_set_class(ctx_, 0));
+  ++iter_;
+  return false;
+}
+
 bool GBDT::TrainOneIter(const float* grad, const float* hess) {
+  if (is_rf_) {
+    if (grad != nullptr || hess != nullptr) Log::Fatal("RF mode do not support custom objective function, please use built-in objectives.");
+    return RFTrainOneIter();
+  }
   const int N = train_->num_data();
   const int K = num_tree_per_iteration_;
   std::vector<double> init_scores(K, 0.0);
@@ -346,36 +470,7 @@ bool GBDT::TrainOneIter(const float* grad, const float* hess) {
       Check(lgbcu_train_tree(ctx_, records_.data(), &ns));
       st.tick("lgbcu_train_tree");
       tree.reset(new Tree(config_.num_leaves));
-      std::vector<uint32_t> cat_sets;   // the tree's categorical bin sets (8 words each), if it has any
-      if (has_categorical_) {
-        int32_t nsets = 0;
-        Check(lgbcu_tree_cat_sets(ctx_, nullptr, 0, &nsets));
-        if (nsets > 0) { cat_sets.resize(static_cast<size_t>(nsets) * 8); Check(lgbcu_tree_cat_sets(ctx_, cat_sets.data(), nsets, &nsets)); }
-      }
-      for (int i = 0; i < ns; ++i) {
-        const LgbCuSplitRecord& r = records_[i];
-        const BinMapper& m = train_->mapper(r.feature);
-        if (m.is_categorical()) {
-          // SerialTreeLearner::SplitInner, categorical branch (serial_tree_learner.cpp:592-621): the record names its set
-          // of bins; the model carries the set of the bins' category values
-          if (r.threshold < 0 || static_cast<size_t>(r.threshold) * 8 + 8 > cat_sets.size()) Log::Fatal("categorical split names bin set %d of %d", r.threshold, static_cast<int>(cat_sets.size() / 8));
-          const uint32_t* bin_set = cat_sets.data() + static_cast<size_t>(r.threshold) * 8;
-          std::vector<uint32_t> cat_set;   // Common::ConstructBitset over RealThreshold(bin)
-          for (int b = 0; b < m.num_bin(); ++b) {
-            if (!((bin_set[b >> 5] >> (b & 31)) & 1u)) continue;
-            const int v = static_cast<int>(m.BinToValue(b));
-            const int i1 = v / 32, i2 = v % 32;
-            if (static_cast<int>(cat_set.size()) < i1 + 1) cat_set.resize(i1 + 1, 0);
-            cat_set[i1] |= (1u << i2);
-          }
-          tree->SplitCategorical(r.leaf, r.feature, r.real_feature, bin_set, cat_set, r.left_output, r.right_output, r.left_count,
-                                 r.right_count, r.left_sum_hessian, r.right_sum_hessian, r.gain, m.missing_type());
-          continue;
-        }
-        tree->Split(r.leaf, r.feature, r.real_feature, static_cast<uint32_t>(r.threshold), m.BinToValue(r.threshold),
-                    r.left_output, r.right_output, r.left_count, r.right_count, r.left_sum_hessian, r.right_sum_hessian,
-                    r.gain, m.missing_type(), r.default_left != 0);
-      }
+      ReplayRecords(tree.get(), ns);
     }
     if (tree->num_leaves() > 1) {
       should_continue = true;
@@ -758,6 +853,7 @@ void GBDT::PredictMat(const void* data, int data_type, int32_t nrow, int32_t nco
       // GBDT::PredictRaw (gbdt_prediction.cpp:13-31): tree i * K + k adds to class k; a row's K outputs are adjacent
       for (int k = 0; k < K; ++k) s[k] = 0.0;
       for (int it = 0; it < n_iter; ++it) for (int k = 0; k < K; ++k) s[k] += models_[static_cast<size_t>(it) * K + k]->Predict(row.data());
+      if (is_rf_ && !raw_score) for (int k = 0; k < K; ++k) s[k] /= n_iter;   // average_output_: GBDT::Predict divides, PredictRaw does not (gbdt_prediction.cpp:13-31, 55-60)
       if (!raw_score && objective_) { objective_->ConvertOutput(s.data(), conv.data()); for (int k = 0; k < K; ++k) s[k] = conv[k]; }
       for (int k = 0; k < K; ++k) out[static_cast<size_t>(r) * K + k] = s[k];
     }
@@ -831,10 +927,16 @@ std::string GBDT::SaveModelToString(int start_iteration, int num_iteration) cons
   ss << "label_index=0" << '\n';
   ss << "max_feature_idx=" << train_->num_total_features() - 1 << '\n';
   if (objective_) ss << "objective=" << objective_->ToString() << '\n';
+  if (is_rf_) ss << "average_output" << '\n';
   {
     std::string names;
     for (size_t i = 0; i < train_->feature_names().size(); ++i) { if (i) names += ' '; names += train_->feature_names()[i]; }
     ss << "feature_names=" << names << '\n';
+    if (!config_.monotone_constraints.empty()) {   // gbdt_model_text.cpp:329-332
+      ss << "monotone_constraints=";
+      for (size_t i = 0; i < config_.monotone_constraints.size(); ++i) { if (i) ss << ' '; ss << static_cast<int>(config_.monotone_constraints[i]); }
+      ss << '\n';
+    }
     std::string infos; const auto fi = train_->feature_infos();
     for (size_t i = 0; i < fi.size(); ++i) { if (i) infos += ' '; infos += fi[i]; }
     ss << "feature_infos=" << infos << '\n';

@@ -41,6 +41,7 @@ class GBDT {
   int valid_num_data(int idx) const { return valid_[idx].data->num_data(); }
   void GetValidScore(int idx, double* out, bool converted) const;  // LGBM_BoosterGetPredict(data_idx = idx + 1)
   std::vector<double> GetEvalAt(int data_idx);
+  bool average_output() const { return is_rf_; }
   std::vector<std::string> EvalNames() const;
   void PredictMat(const void* data, int data_type, int32_t nrow, int32_t ncol, bool row_major, bool raw_score,
                   int num_iteration, double* out) const;
@@ -74,6 +75,14 @@ class GBDT {
   void DroppingTrees();
   void Normalize();
   void AddTreeToTrain(const Tree& tree, int class_id);   // ScoreUpdater::AddScore(tree, class) over every training row
+  // boosting=rf (src/boosting/rf.hpp:25-215): gradients taken once at the initial scores, every tree on a fresh bag at
+  // shrinkage 1, the scores kept as the running mean of the trees, predictions averaged (average_output)
+  bool is_rf_ = false;
+  std::vector<double> rf_init_scores_;
+  void ReplayRecords(Tree* tree, int num_splits);
+  void RFInit();
+  bool RFTrainOneIter();
+  void MultiplyScore(int class_id, double val);
   bool has_categorical_ = false;   // some feature of the training data is categorical
   std::vector<MetricSpec> metrics_;
   std::vector<int> eval_at_;

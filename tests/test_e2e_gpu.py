@@ -198,7 +198,7 @@ def test_errors_surface_through_last_error():
     with pytest.raises(capi.LGBMError):
         ours.booster_create(ds, "objective=rank_xendcg")
     with pytest.raises(capi.LGBMError):
-        ours.booster_create(ds, "objective=binary boosting=rf")
+        ours.booster_create(ds, "objective=binary boosting=gbdt tree_learner=voting")
     with pytest.raises(capi.LGBMError):
         ours.set_field(ds, "label", y[:10])
 
