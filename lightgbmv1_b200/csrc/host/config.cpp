@@ -266,6 +266,14 @@ void Config::Set(const std::unordered_map<std::string, std::string>& p) {
       categorical_feature.push_back(static_cast<int>(v));
     }
   }
+  if (GetStr(p, "max_bin_by_feature", &s) && !s.empty()) {
+    max_bin_by_feature.clear();
+    for (double d : ParseDoubles(s)) max_bin_by_feature.push_back(static_cast<int>(d));
+    for (int v : max_bin_by_feature) {
+      if (v <= 1) Log::Fatal("Check failed: (*(std::min_element(max_bin_by_feature.begin(), max_bin_by_feature.end()))) > (1)");
+      if (v > 65535) Log::Fatal("max_bin_by_feature should be <= 65535 (8- and 16-bit bins are built), got %d", v);
+    }
+  }
   GetDouble(p, "drop_rate", &drop_rate);
   GetDouble(p, "skip_drop", &skip_drop);
   GetInt(p, "max_drop", &max_drop);
@@ -343,7 +351,7 @@ void Config::Set(const std::unordered_map<std::string, std::string>& p) {
   GetDouble(p, "monotone_penalty", &monotone_penalty);
   if (monotone_penalty < 0.0) Log::Fatal("monotone_penalty should be >= 0");
   for (const char* k : {"forcedsplits_filename", "forcedbins_filename", "interaction_constraints",
-                        "cegb_penalty_feature_lazy", "cegb_penalty_feature_coupled", "max_bin_by_feature",
+                        "cegb_penalty_feature_lazy", "cegb_penalty_feature_coupled",
                         "linear_tree"}) {
     if (GetStr(p, k, &s)) Log::Fatal("parameter %s is outside this library's path", k);
   }

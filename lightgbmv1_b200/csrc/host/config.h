@@ -61,6 +61,7 @@ struct Config {
   std::vector<int> categorical_feature;
   int min_data_per_group = 100, max_cat_threshold = 32, max_cat_to_onehot = 4;
   double cat_l2 = 10.0, cat_smooth = 10.0;
+  std::vector<int> max_bin_by_feature;   // per raw column; empty = max_bin everywhere
   // boosting=dart (src/boosting/dart.hpp)
   double drop_rate = 0.1, skip_drop = 0.5;
   int max_drop = 50, drop_seed = 4;

@@ -278,12 +278,15 @@ Dataset* Dataset::FromDenseMatrix(const void* data, int data_type, int32_t nrow,
   st.tick("sample rows");
   // bin mappers (DatasetLoader::ConstructFromSampleData, src/io/dataset_loader.cpp:527-585)
   const data_size_t filter_cnt = static_cast<data_size_t>(static_cast<double>(config.min_data_in_leaf * static_cast<size_t>(sample_cnt)) / nrow);
+  if (!config.max_bin_by_feature.empty() && static_cast<int>(config.max_bin_by_feature.size()) != ncol)
+    Log::Fatal("Check failed: (static_cast<size_t>(num_col)) == (config_.max_bin_by_feature.size())");   // dataset_loader.cpp:534-537
   std::vector<std::shared_ptr<BinMapper>> all(ncol);
 #pragma omp parallel for schedule(guided)
   for (int c = 0; c < ncol; ++c) {
     all[c].reset(new BinMapper());
     const bool categorical = std::find(config.categorical_feature.begin(), config.categorical_feature.end(), c) != config.categorical_feature.end();
-    all[c]->FindBin(sample_vals[c], static_cast<size_t>(sample_cnt), config.max_bin, config.min_data_in_bin, filter_cnt,
+    all[c]->FindBin(sample_vals[c], static_cast<size_t>(sample_cnt), config.max_bin_by_feature.empty() ? config.max_bin : config.max_bin_by_feature[c],
+                    config.min_data_in_bin, filter_cnt,
                     config.feature_pre_filter, config.use_missing, config.zero_as_missing, categorical);
   }
   st.tick("FindBin");

@@ -78,6 +78,7 @@ def feature_infos(lib_handle, fn_num, fn_info, ds):
     "max_bin=255 zero_as_missing=true verbosity=-1",
     "max_bin=255 use_missing=false verbosity=-1",
     "max_bin=255 enable_bundle=false verbosity=-1",
+    "max_bin=255 max_bin_by_feature=255,7,3,31,100,2,16,200,9,40,63,5 verbosity=-1",
     "max_bin=255 bin_construct_sample_cnt=1500 data_random_seed=7 verbosity=-1",
     "max_bin=255 feature_pre_filter=false min_data_in_leaf=3000 verbosity=-1",
 ])
