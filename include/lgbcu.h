@@ -380,6 +380,8 @@ LGBCU_API int lgbcu_valid_copy_score(LgbCuContext* ctx, int32_t set, double* out
 #define LGBCU_METRIC_TWEEDIE 13        /* `sigmoid` = tweedie_variance_power */
 #define LGBCU_METRIC_BINARY_ERROR 14   /* `sigmoid` as for binary_logloss */
 #define LGBCU_METRIC_MAPE 16
+#define LGBCU_METRIC_MAP 18            /* map@k per eval position (map_metric.hpp); uses the tables of lgbcu_eval_set_ndcg */
+#define LGBCU_METRIC_GAMMA_DEVIANCE 19
 #define LGBCU_METRIC_XENTLAMBDA 17     /* cross_entropy_lambda: the weight sits inside the loss, the mean is over the rows */
 #define LGBCU_METRIC_XENTROPY 15       /* cross_entropy (labels in [0, 1]); `sigmoid` as for binary_logloss.  kullback_leibler is
                                         * this plus a constant of the labels, which the host adds */

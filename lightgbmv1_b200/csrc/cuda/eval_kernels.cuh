@@ -70,6 +70,10 @@ __global__ void __launch_bounds__(EVAL_THREADS) k_eval_pointwise(int n, int kind
       b *= 1.0f - prob > log_arg_epsilon ? log(1.0f - prob) : log(log_arg_epsilon);
       acc += -(a + b);
       continue;
+    } else if (kind == 13) {         // GammaDevianceMetric::LossOnPoint (regression_metric.hpp:284-288)
+      const double t = conv_exp ? exp(s) : s;
+      const double tmp = y / (t + 1.0e-9);
+      loss = tmp - safe_log(tmp) - 1;
     } else if (kind == 11) {         // MAPEMetric::LossOnPoint (regression_metric.hpp:248-250)
       loss = fabs(y - s) / fmaxf(1.0f, fabsf(y));
     } else if (kind == 10) {         // XentLoss (xentropy_metric.hpp:34-50) of the converted score
@@ -237,6 +241,51 @@ __global__ void __launch_bounds__(EVAL_THREADS) k_ndcg(int num_queries, const in
         int k = eval_at[e]; if (k > cnt) k = cnt;
         for (int j = left; j < k; ++j) cur += s_contrib[j];
         out[e] = cur * inv_max_dcg[(size_t)q * num_eval + e] * w;
+        left = k;
+      }
+    }
+    __syncthreads();
+  }
+}
+
+// ---- MAP@k (MapMetric::CalMapAtK, map_metric.hpp:72-103): one block per query, ranks as for NDCG (a stable descending
+//      sort), then one thread walks the top documents: every hit adds (hits so far) / (position + 1).
+__global__ void __launch_bounds__(EVAL_THREADS) k_map(int num_queries, const int* __restrict__ qb, const double* __restrict__ score,
+                                                      const float* __restrict__ label, const float* __restrict__ query_weight,
+                                                      const int* __restrict__ eval_at, int num_eval, int max_k,
+                                                      double* __restrict__ per_query) {
+  __shared__ unsigned char s_hit[NDCG_MAX_K];
+  __shared__ int s_npos;
+  for (int q = blockIdx.x; q < num_queries; q += gridDim.x) {
+    const int b = qb[q], cnt = qb[q + 1] - b;
+    double* out = per_query + (size_t)q * num_eval;
+    const double w = query_weight ? (double)query_weight[q] : 1.0;
+    const int kk = max_k < cnt ? max_k : cnt;
+    if (threadIdx.x == 0) s_npos = 0;
+    for (int r = threadIdx.x; r < kk; r += blockDim.x) s_hit[r] = 0;
+    __syncthreads();
+    int my_pos = 0;
+    for (int i = threadIdx.x; i < cnt; i += blockDim.x) {
+      const double si = score[b + i];
+      int rank = 0;
+      for (int j = 0; j < cnt; ++j) {
+        const double sj = score[b + j];
+        rank += (sj > si) || (sj == si && j < i);
+      }
+      const bool hit = label[b + i] > 0.5f;
+      my_pos += hit ? 1 : 0;
+      if (rank < kk && hit) s_hit[rank] = 1;
+    }
+    if (my_pos) atomicAdd(&s_npos, my_pos);
+    __syncthreads();
+    if (threadIdx.x == 0) {
+      const int npos = s_npos;
+      int num_hit = 0, left = 0;
+      double sum_ap = 0.0f;
+      for (int e = 0; e < num_eval; ++e) {
+        int k = eval_at[e]; if (k > cnt) k = cnt;
+        for (int j = left; j < k; ++j) if (s_hit[j]) { ++num_hit; sum_ap += (double)num_hit / (j + 1.0f); }
+        out[e] = (npos > 0 ? sum_ap / (npos < k ? npos : k) : 1.0) * w;
         left = k;
       }
     }

@@ -246,7 +246,7 @@ int eval_auc(LgbCuContext* c, int n, const double* score, const float* label, co
 
 int lgbcu_eval(LgbCuContext* c, int32_t set, int32_t kind, double sigmoid, double* out, int32_t out_len) {
   NEED(c && out && out_len >= 1, "lgbcu_eval: bad argument");
-  NEED(kind >= LGBCU_METRIC_L2 && kind <= LGBCU_METRIC_XENTLAMBDA, "lgbcu_eval: unknown metric kind %d", kind);
+  NEED(kind >= LGBCU_METRIC_L2 && kind <= LGBCU_METRIC_GAMMA_DEVIANCE, "lgbcu_eval: unknown metric kind %d", kind);
   USE_DEVICE(c->device);
   int n; const double* score; const float* label; const float* weight; const int* query; int nq; NdcgTables* nd;
   if (set < 0) {
@@ -261,6 +261,20 @@ int lgbcu_eval(LgbCuContext* c, int32_t set, int32_t kind, double sigmoid, doubl
   }
   NEED(label, "lgbcu_eval: the data set has no label");
   if (eval_scratch(c)) return -1;
+  if (kind == LGBCU_METRIC_MAP) {
+    NEED(nd->ready && query && nq > 0, "The MAP metric requires query information");
+    NEED(out_len >= nd->num_eval, "lgbcu_eval: out_len %d < %d evaluation positions", out_len, nd->num_eval);
+    const size_t need = (size_t)nq * nd->num_eval;
+    if (c->ndcg_cap < need) { CU(dev_alloc(&c->d_ndcg_per_query, need)); c->ndcg_cap = need; }
+    LAUNCH(k_map, std::min(nq, c->num_sms * 8), EVAL_THREADS, 0, c->stream, nq, query, score, label, nd->d_query_weight,
+           nd->d_eval_at, nd->num_eval, nd->max_k, c->d_ndcg_per_query);
+    LAUNCH(k_eval_final, 1, EVAL_THREADS, 0, c->stream, nq, nd->num_eval, c->d_ndcg_per_query, c->d_eval_out);
+    CU(cudaGetLastError());
+    CU(cudaMemcpyAsync(c->h_eval_out, c->d_eval_out, sizeof(double) * nd->num_eval, cudaMemcpyDeviceToHost, c->stream));
+    CU(cudaStreamSynchronize(c->stream));
+    for (int e = 0; e < nd->num_eval; ++e) out[e] = c->h_eval_out[e] / nd->sum_query_weights;
+    return 0;
+  }
   if (kind == LGBCU_METRIC_NDCG) {
     NEED(nd->ready && query && nq > 0, "The NDCG metric requires query information");
     NEED(out_len >= nd->num_eval, "lgbcu_eval: out_len %d < %d evaluation positions", out_len, nd->num_eval);
@@ -298,7 +312,7 @@ int lgbcu_eval(LgbCuContext* c, int32_t set, int32_t kind, double sigmoid, doubl
   const int pk = kind == LGBCU_METRIC_BINARY_LOGLOSS ? 1 : kind == LGBCU_METRIC_L1 ? 2 : kind == LGBCU_METRIC_QUANTILE ? 3 :
                  kind == LGBCU_METRIC_HUBER ? 4 : kind == LGBCU_METRIC_FAIR ? 5 : kind == LGBCU_METRIC_POISSON ? 6 :
                  kind == LGBCU_METRIC_GAMMA ? 7 : kind == LGBCU_METRIC_TWEEDIE ? 8 : kind == LGBCU_METRIC_BINARY_ERROR ? 9 :
-                 kind == LGBCU_METRIC_XENTROPY ? 10 : kind == LGBCU_METRIC_MAPE ? 11 : kind == LGBCU_METRIC_XENTLAMBDA ? 12 : 0;
+                 kind == LGBCU_METRIC_XENTROPY ? 10 : kind == LGBCU_METRIC_MAPE ? 11 : kind == LGBCU_METRIC_XENTLAMBDA ? 12 : kind == LGBCU_METRIC_GAMMA_DEVIANCE ? 13 : 0;
   // metrics see the objective's ConvertOutput: exp for the log-link objectives
   const int conv_exp = (c->objective == LGBCU_OBJ_POISSON || c->objective == LGBCU_OBJ_GAMMA || c->objective == LGBCU_OBJ_TWEEDIE) ? 1 : 0;
   LAUNCH(k_eval_pointwise, grid, EVAL_THREADS, 0, c->stream, n, pk, sigmoid, conv_exp, score,
@@ -308,7 +322,8 @@ int lgbcu_eval(LgbCuContext* c, int32_t set, int32_t kind, double sigmoid, doubl
   CU(cudaMemcpyAsync(c->h_eval_out, c->d_eval_out, sizeof(double), cudaMemcpyDeviceToHost, c->stream));
   CU(cudaStreamSynchronize(c->stream));
   // (cross_entropy_lambda keeps the weight inside the loss and averages over the rows: xentropy_metric.hpp:224)
-  const double avg = c->h_eval_out[0] / (kind == LGBCU_METRIC_XENTLAMBDA ? (double)n : sum_w);
+  double avg = c->h_eval_out[0] / (kind == LGBCU_METRIC_XENTLAMBDA ? (double)n : sum_w);
+  if (kind == LGBCU_METRIC_GAMMA_DEVIANCE) avg = c->h_eval_out[0] * 2;   // GammaDevianceMetric::AverageLoss: the sum, doubled
   out[0] = kind == LGBCU_METRIC_RMSE ? std::sqrt(avg) : avg;
   return 0;
 }

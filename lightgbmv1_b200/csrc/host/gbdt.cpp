@@ -137,6 +137,11 @@ GBDT::GBDT(const Dataset* train, const Config& config)
       spec.kind = LGBCU_METRIC_NDCG;
       for (int k : eval_at_) spec.names.push_back("ndcg@" + std::to_string(k));
     }
+    else if (m == "map") {
+      spec.kind = LGBCU_METRIC_MAP;
+      for (int k : eval_at_) spec.names.push_back("map@" + std::to_string(k));
+    }
+    else if (m == "gamma_deviance") { spec.kind = LGBCU_METRIC_GAMMA_DEVIANCE; spec.names = {"gamma_deviance"}; }
     else if (m == "l1") { spec.kind = LGBCU_METRIC_L1; spec.names = {"l1"}; }
     else if (m == "huber") { spec.kind = LGBCU_METRIC_HUBER; spec.names = {"huber"}; }
     else if (m == "fair") { spec.kind = LGBCU_METRIC_FAIR; spec.names = {"fair"}; }
@@ -154,7 +159,7 @@ GBDT::GBDT(const Dataset* train, const Config& config)
     else if (m == "cross_entropy") { spec.kind = LGBCU_METRIC_XENTROPY; spec.names = {"cross_entropy"}; }
     else if (m == "kullback_leibler") { spec.kind = LGBCU_METRIC_XENTROPY; spec.names = {"kullback_leibler"}; spec.kl = true; }
     else if (m == "custom") continue;
-    else Log::Fatal("metric=%s is outside this library's path (l2, rmse, l1, huber, fair, poisson, gamma, tweedie, quantile, mape, binary_logloss, binary_error, cross_entropy, cross_entropy_lambda, kullback_leibler, auc, ndcg, multi_logloss, multi_error)", m.c_str());
+    else Log::Fatal("metric=%s is outside this library's path (l2, rmse, l1, huber, fair, poisson, gamma, tweedie, quantile, mape, gamma_deviance, map, binary_logloss, binary_error, cross_entropy, cross_entropy_lambda, kullback_leibler, auc, ndcg, multi_logloss, multi_error)", m.c_str());
     if ((spec.kind == LGBCU_METRIC_MULTI_LOGLOSS || spec.kind == LGBCU_METRIC_MULTI_ERROR) != (num_tree_per_iteration_ > 1))
       Log::Fatal("Multiclass objective and metrics don't match");
     metrics_.push_back(spec);
@@ -672,7 +677,7 @@ void GBDT::AddValidData(const Dataset* valid) {
   }
   Check(lgbcu_set_class(ctx_, 0));
   for (const MetricSpec& m : metrics_) {
-    if (m.kind == LGBCU_METRIC_NDCG) SetupNdcg(e.set, md, n);
+    if (m.kind == LGBCU_METRIC_NDCG || m.kind == LGBCU_METRIC_MAP) SetupNdcg(e.set, md, n);
     if (md.label.empty()) Log::Fatal("Label should not be NULL");
   }
 }
@@ -760,7 +765,7 @@ std::vector<double> GBDT::GetEvalAt(int data_idx) {
   const int set = data_idx == 0 ? -1 : valid_[data_idx - 1].set;
   std::vector<double> ret;
   for (const MetricSpec& m : metrics_) {
-    if (m.kind == LGBCU_METRIC_NDCG && data_idx == 0 && !train_ndcg_ready_) {
+    if ((m.kind == LGBCU_METRIC_NDCG || m.kind == LGBCU_METRIC_MAP) && data_idx == 0 && !train_ndcg_ready_) {
       SetupNdcg(-1, train_->metadata(), train_->num_data());
       train_ndcg_ready_ = true;
     }

@@ -115,6 +115,45 @@ def test_lambdarank_ndcg(weighted):
     _compare(ref, ours)
 
 
+@pytest.mark.parametrize("weighted", [False, True])
+def test_lambdarank_map_beside_ndcg(weighted):
+    """MapMetric (map_metric.hpp): map@k on the device beside ndcg@k, binary relevance, a query without positives = 1"""
+    rng = np.random.default_rng(14)
+    def make(nq):
+        sizes = rng.integers(1, 40, size=nq).astype(np.int32)
+        n = int(sizes.sum())
+        X = rng.standard_normal((n, 10)).astype(np.float32)
+        rel = X[:, 0] + 0.5 * X[:, 1] + 0.5 * rng.standard_normal(n)
+        y = (rel > 0.6).astype(np.float32)
+        y[: sizes[0]] = 0
+        return X, y, sizes
+    Xt, yt, qt = make(500)
+    Xv, yv, qv = make(250)
+    wt = (rng.random(len(yt)) + 0.5).astype(np.float32) if weighted else None
+    wv = (rng.random(len(yv)) + 0.5).astype(np.float32) if weighted else None
+    params = ("objective=lambdarank metric=map,ndcg eval_at=1,2,5,20 num_leaves=15 min_data_in_leaf=10 "
+              "learning_rate=0.1 verbosity=-1")
+    ref = _run(capi.reference(), Xt, yt, Xv, yv, params, 6, wt, wv, qt, qv, extra=REF_EXTRA)
+    ours = _run(capi.ours(), Xt, yt, Xv, yv, params, 6, wt, wv, qt, qv)
+    assert ref[0] == ["map@1", "map@2", "map@5", "map@20", "ndcg@1", "ndcg@2", "ndcg@5", "ndcg@20"]
+    _compare(ref, ours)
+
+
+def test_gamma_deviance_metric():
+    rng = np.random.default_rng(15)
+    def make(n):
+        X = rng.standard_normal((n, 8)).astype(np.float32)
+        y = (rng.gamma(2.0, np.exp(0.3 * X[:, 0] - 0.2 * X[:, 1]) / 2.0) + 1e-3).astype(np.float32)
+        return X, y
+    Xt, yt = make(20_000); Xv, yv = make(6_000)
+    wt = (rng.random(len(yt)) + 0.5).astype(np.float32); wv = (rng.random(len(yv)) + 0.5).astype(np.float32)
+    params = "objective=gamma metric=gamma,gamma_deviance num_leaves=15 min_data_in_leaf=20 learning_rate=0.1 verbosity=-1"
+    ref = _run(capi.reference(), Xt, yt, Xv, yv, params, 6, wt, wv, extra=REF_EXTRA)
+    ours = _run(capi.ours(), Xt, yt, Xv, yv, params, 6, wt, wv)
+    assert ref[0] == ["gamma", "gamma_deviance"]
+    _compare(ref, ours)
+
+
 def test_misaligned_valid_set_and_unknown_metric_are_errors():
     ours = capi.ours()
     X, y = higgs_like(1, 5_000)
@@ -124,4 +163,4 @@ def test_misaligned_valid_set_and_unknown_metric_are_errors():
     with pytest.raises(capi.LGBMError, match="different bin mappers"):
         ours.add_valid(b, dv)
     with pytest.raises(capi.LGBMError, match="outside this library's path"):
-        ours.booster_create(dt, "objective=binary metric=map verbosity=-1")
+        ours.booster_create(dt, "objective=binary metric=auc_mu verbosity=-1")
