@@ -49,7 +49,8 @@ enum { LGBCU_OBJ_NONE = 0, LGBCU_OBJ_BINARY = 1, LGBCU_OBJ_L2 = 2, LGBCU_OBJ_LAM
        LGBCU_OBJ_GAMMA = 11, LGBCU_OBJ_TWEEDIE = 12 /* p0 = tweedie_variance_power */,
        LGBCU_OBJ_XENTROPY = 13 /* cross_entropy: labels in [0, 1] */,
        LGBCU_OBJ_MAPE = 14 /* L1 with the per-row weight 1 / max(1, |label|); no user weights */,
-       LGBCU_OBJ_XENTLAMBDA = 15 /* cross_entropy_lambda */ };
+       LGBCU_OBJ_XENTLAMBDA = 15 /* cross_entropy_lambda */,
+       LGBCU_OBJ_XENDCG = 16 /* rank_xendcg: p0 = objective_seed; needs lgbcu_set_query */ };
 /* histogram kernel selection (LGBCU_HIST_AUTO picks by leaf size) */
 enum { LGBCU_HIST_AUTO = 0, LGBCU_HIST_GLOBAL_ATOMIC = 1, LGBCU_HIST_WARP_PRIVATE = 2 };
 

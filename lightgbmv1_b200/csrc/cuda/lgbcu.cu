@@ -220,6 +220,8 @@ struct LgbCuContext {
   bool any_cat = false, general = false; int cat_features = 0;
   // monotone constraints (basic method): per-feature types on the device; every feature then takes the general search
   bool use_mc = false; signed char* d_monotone = nullptr; double mc_penalty = 0.0;
+  // rank_xendcg: one LCG state per query (seeded objective_seed + query), two doubles of scratch per document
+  unsigned* d_xe_rng = nullptr; double* d_xe_rho = nullptr; double* d_xe_par = nullptr; bool xe_ready = false;
   int wide_smem_slots = 0;   // slots of a feature's histogram that k_hist_wide keeps in shared memory
   unsigned* d_cat_pool = nullptr; int cat_cap = 0;
   unsigned* d_tree_cat = nullptr; int tree_cat_count = 0, tree_cat_cap = 0;
@@ -730,6 +732,8 @@ int lgbcu_destroy(LgbCuContext* c) {
   free_valid_sets(c);
   if (c->d_cat_pool) { lgb_dev_free(c->d_cat_pool); c->d_cat_pool = nullptr; }
   if (c->d_monotone) { lgb_dev_free(c->d_monotone); c->d_monotone = nullptr; }
+  for (void* q : {(void*)c->d_xe_rng, (void*)c->d_xe_rho, (void*)c->d_xe_par}) if (q) lgb_dev_free(q);
+  c->d_xe_rng = nullptr; c->d_xe_rho = nullptr; c->d_xe_par = nullptr;
   if (c->d_tree_cat) { lgb_dev_free(c->d_tree_cat); c->d_tree_cat = nullptr; }
   void* ptrs[] = {c->d_bins, c->d_feats, c->d_feat_used, c->d_grad_base, c->d_hess_base, c->d_gh, c->d_label, c->d_weight, c->d_score_base,
                   c->d_indices[0], c->d_indices[1], c->d_part_bits, c->d_part_sync, c->d_bins_col, c->d_query, c->d_label_gain,
@@ -939,6 +943,7 @@ int lgbcu_set_query(LgbCuContext* c, const int32_t* boundaries, int32_t num_quer
     c->max_query = std::max(c->max_query, boundaries[q + 1] - boundaries[q]);
   }
   CU(dev_alloc(&c->d_query, (size_t)num_queries + 1));
+  c->xe_ready = false;
   CU(cudaMemcpyAsync(c->d_query, boundaries, sizeof(int) * (num_queries + 1), cudaMemcpyHostToDevice, c->stream));
   CU(cudaStreamSynchronize(c->stream));
   c->rank_ready = false;
@@ -947,10 +952,10 @@ int lgbcu_set_query(LgbCuContext* c, const int32_t* boundaries, int32_t num_quer
 
 int lgbcu_set_objective(LgbCuContext* c, int kind, double p0, double p1, double p2) {
   NEED(c, "lgbcu: NULL context");
-  NEED(kind >= LGBCU_OBJ_NONE && kind <= LGBCU_OBJ_XENTLAMBDA, "lgbcu_set_objective: unknown kind %d", kind);
+  NEED(kind >= LGBCU_OBJ_NONE && kind <= LGBCU_OBJ_XENDCG, "lgbcu_set_objective: unknown kind %d", kind);
   if (kind == LGBCU_OBJ_BINARY || kind == LGBCU_OBJ_LAMBDARANK) NEED(p0 > 0, "Sigmoid parameter %f should be greater than zero", p0);
   c->objective = kind; c->obj_p[0] = p0; c->obj_p[1] = p1; c->obj_p[2] = p2;
-  c->rank_ready = false;
+  c->rank_ready = false; c->xe_ready = false;
   return 0;
 }
 
@@ -1012,6 +1017,19 @@ int lgbcu_get_gradients(LgbCuContext* c) {
   } else if (c->objective == LGBCU_OBJ_LAMBDARANK) {
     if (rank_prepare(c)) return -1;
     if (rank_launch(c)) return -1;
+  } else if (c->objective == LGBCU_OBJ_XENDCG) {
+    NEED(c->d_query && c->num_queries > 0, "Ranking tasks require query information");
+    if (!c->xe_ready) {
+      std::vector<unsigned> st((size_t)c->num_queries);
+      for (int q = 0; q < c->num_queries; ++q) st[q] = (unsigned)((int)c->obj_p[0] + q);   // Random(seed_ + i)
+      CU(dev_alloc(&c->d_xe_rng, (size_t)c->num_queries));
+      CU(dev_alloc(&c->d_xe_rho, (size_t)c->N)); CU(dev_alloc(&c->d_xe_par, (size_t)c->N));
+      CU(cudaMemcpyAsync(c->d_xe_rng, st.data(), sizeof(unsigned) * st.size(), cudaMemcpyHostToDevice, c->stream));
+      CU(cudaStreamSynchronize(c->stream));
+      c->xe_ready = true;
+    }
+    LAUNCH(k_grad_xendcg, grid_for(c, c->num_queries, 128), 128, 0, c->stream, c->num_queries, c->d_query, c->d_score, c->d_label, w,
+           c->d_xe_rng, c->d_xe_rho, c->d_xe_par, c->d_grad, c->d_hess);
   } else if (c->objective == LGBCU_OBJ_MULTICLASSOVA) {
     NEED((int)c->obj_p[0] == c->num_class && (int)c->ova_w.size() == 2 * c->num_class, "lgbcu_get_gradients: multiclassova needs lgbcu_set_num_class and lgbcu_set_ova_label_weights");
     for (int k = 0; k < c->num_class; ++k) {   // one BinaryLogloss per class on its own planes

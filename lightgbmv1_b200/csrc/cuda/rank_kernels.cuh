@@ -244,3 +244,60 @@ int rank_launch(LgbCuContext* c) {
 }
 
 }  // namespace
+
+// ---- rank_xendcg (RankXENDCG::GetGradientsForOneQuery, src/objective/rank_objective.hpp:304-356) -------------------
+// One thread per query walks the reference's loops in their order (softmax of the scores, the randomised gains
+// Phi(label, u) with u from the query's own LCG -- utils/random.h, seeded objective_seed + query and advanced one draw
+// per document per iteration --, then the three accumulation passes).  rho / params = scratch of one double per
+// document each.  The sums are sequential in the reference, so they are here.
+__global__ void k_grad_xendcg(int num_queries, const int* __restrict__ qb, const double* __restrict__ score, const float* __restrict__ label,
+                              const float* __restrict__ weight, unsigned* __restrict__ rng, double* __restrict__ rho_all,
+                              double* __restrict__ params_all, float* __restrict__ grad, float* __restrict__ hess) {
+  for (int q = blockIdx.x * blockDim.x + threadIdx.x; q < num_queries; q += gridDim.x * blockDim.x) {
+    const int b = qb[q], cnt = qb[q + 1] - b;
+    float* lambdas = grad + b; float* hessians = hess + b;
+    if (cnt <= 1) {
+      for (int i = 0; i < cnt; ++i) { lambdas[i] = 0.0f; hessians[i] = 0.0f; }
+    } else {
+      const double* sc = score + b; const float* lab = label + b;
+      double* rho = rho_all + b; double* params = params_all + b;
+      double wmax = sc[0];   // Common::Softmax
+      for (int i = 1; i < cnt; ++i) wmax = fmax(sc[i], wmax);
+      double wsum = 0.0f;
+      for (int i = 0; i < cnt; ++i) { rho[i] = exp(sc[i] - wmax); wsum += rho[i]; }
+      for (int i = 0; i < cnt; ++i) rho[i] /= wsum;
+      unsigned x = rng[q];
+      double inv_denominator = 0;
+      for (int i = 0; i < cnt; ++i) {
+        x = 214013u * x + 2531011u;                                         // Random::NextFloat
+        const double g = (double)((float)((x >> 16) & 0x7FFF) / 32768.0f);
+        params[i] = ldexp(1.0, (int)lab[i]) - g;                            // Phi: 2^label - u
+        inv_denominator += params[i];
+      }
+      rng[q] = x;
+      inv_denominator = 1. / fmax(LGB_EPS, inv_denominator);
+      double sum_l1 = 0.0;
+      for (int i = 0; i < cnt; ++i) {
+        const double term = -params[i] * inv_denominator + rho[i];
+        lambdas[i] = (float)term;
+        params[i] = term / (1. - rho[i]);
+        sum_l1 += params[i];
+      }
+      double sum_l2 = 0.0;
+      for (int i = 0; i < cnt; ++i) {
+        const double term = rho[i] * (sum_l1 - params[i]);
+        lambdas[i] += (float)term;
+        params[i] = term / (1. - rho[i]);
+        sum_l2 += params[i];
+      }
+      for (int i = 0; i < cnt; ++i) {
+        lambdas[i] += (float)(rho[i] * (sum_l2 - params[i]));
+        hessians[i] = (float)(rho[i] * (1.0 - rho[i]));
+      }
+    }
+    if (weight) {   // RankingObjective::GetGradients (:56-62)
+      for (int i = 0; i < cnt; ++i) { lambdas[i] = (float)(lambdas[i] * weight[b + i]); hessians[i] = (float)(hessians[i] * weight[b + i]); }
+    }
+  }
+}
+

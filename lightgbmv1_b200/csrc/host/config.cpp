@@ -120,6 +120,7 @@ std::string ObjectiveAlias(std::string t) {
   if (t == "xentropy" || t == "cross_entropy") return "cross_entropy";
   if (t == "xentlambda" || t == "cross_entropy_lambda") return "cross_entropy_lambda";
   if (t == "mean_absolute_percentage_error" || t == "mape") return "mape";
+  if (t == "rank_xendcg" || t == "xendcg" || t == "xe_ndcg" || t == "xe_ndcg_mart" || t == "xendcg_mart") return "rank_xendcg";
   return t;
 }
 

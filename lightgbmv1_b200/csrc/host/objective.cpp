@@ -131,6 +131,22 @@ class Lambdarank : public Objective {
   double sigmoid_; bool norm_; int trunc_; std::vector<double> label_gain_;
 };
 
+// src/objective/rank_objective.hpp:288-366 (RankXENDCG): cross-entropy ranking with randomised gains
+class RankXendcg : public Objective {
+ public:
+  explicit RankXendcg(const Config& c) : seed_(c.objective_seed) {}
+  void Init(const Metadata& meta, data_size_t, const SumSync&) override {
+    if (meta.query_boundaries.empty()) Log::Fatal("Ranking tasks require query information");
+  }
+  void Configure(LgbCuContext* ctx) const override { Check(lgbcu_set_objective(ctx, LGBCU_OBJ_XENDCG, seed_, 0, 0)); }
+  double BoostFromScore(int) const override { return 0.0; }
+  std::string ToString() const override { return "rank_xendcg"; }
+  const char* Name() const override { return "rank_xendcg"; }
+
+ private:
+  int seed_;
+};
+
 }  // namespace
 
 // PercentileFun / WeightedPercentileFun (src/objective/regression_objective.hpp:18-88) over the labels, for the
@@ -450,6 +466,7 @@ Objective* Objective::Create(const Config& c) {
   if (c.objective == "binary") return new BinaryLogloss(c);
   if (c.objective == "regression") return new RegressionL2(c);
   if (c.objective == "lambdarank") return new Lambdarank(c);
+  if (c.objective == "rank_xendcg") return new RankXendcg(c);
   if (c.objective == "custom") return nullptr;
   Log::Fatal("objective=%s is outside this library's path (binary, regression/l2, regression_l1, huber, fair, poisson, gamma, tweedie, quantile, lambdarank, multiclass, multiclassova, custom)", c.objective.c_str());
 }

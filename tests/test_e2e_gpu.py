@@ -196,7 +196,7 @@ def test_errors_surface_through_last_error():
     ds = ours.dataset_from_mat(X, "verbosity=-1")
     ours.set_field(ds, "label", y)
     with pytest.raises(capi.LGBMError):
-        ours.booster_create(ds, "objective=rank_xendcg")
+        ours.booster_create(ds, "objective=no_such_objective")
     with pytest.raises(capi.LGBMError):
         ours.booster_create(ds, "objective=binary boosting=gbdt tree_learner=voting")
     with pytest.raises(capi.LGBMError):

@@ -139,6 +139,29 @@ def test_lambdarank_map_beside_ndcg(weighted):
     _compare(ref, ours)
 
 
+@pytest.mark.parametrize("weighted", [False, True])
+def test_rank_xendcg_identical_run(weighted):
+    """RankXENDCG (rank_objective.hpp:288-366): the randomised gains come from one LCG per query (objective_seed + query),
+    advanced a draw per document per iteration -- reproduced on the device, so the whole run is the reference's"""
+    rng = np.random.default_rng(24)
+    def make(nq):
+        sizes = rng.integers(1, 60, size=nq).astype(np.int32)
+        n = int(sizes.sum())
+        X = rng.standard_normal((n, 10)).astype(np.float32)
+        rel = X[:, 0] + 0.5 * X[:, 1] + 0.5 * rng.standard_normal(n)
+        y = np.clip(np.floor(rel + 1.5), 0, 4).astype(np.float32)
+        return X, y, sizes
+    Xt, yt, qt = make(700)
+    Xv, yv, qv = make(300)
+    wt = (rng.random(len(yt)) + 0.5).astype(np.float32) if weighted else None
+    wv = (rng.random(len(yv)) + 0.5).astype(np.float32) if weighted else None
+    params = ("objective=rank_xendcg metric=ndcg eval_at=1,5,10 objective_seed=17 num_leaves=15 min_data_in_leaf=10 "
+              "learning_rate=0.1 verbosity=-1")
+    ref = _run(capi.reference(), Xt, yt, Xv, yv, params, 8, wt, wv, qt, qv, extra=REF_EXTRA)
+    ours = _run(capi.ours(), Xt, yt, Xv, yv, params, 8, wt, wv, qt, qv)
+    _compare(ref, ours, rtol=1e-7)
+
+
 def test_gamma_deviance_metric():
     rng = np.random.default_rng(15)
     def make(n):
