@@ -31,6 +31,7 @@ typedef void* BoosterHandle; /* c_api.h:24 */
 #define C_API_DTYPE_INT64 (3)
 #define C_API_PREDICT_NORMAL (0)    /* c_api.h:32-35 */
 #define C_API_PREDICT_RAW_SCORE (1)
+#define C_API_PREDICT_LEAF_INDEX (2)
 
 /* c_api.h:47 */
 LGBM_B200_API const char* LGBM_GetLastError(void);
@@ -53,6 +54,9 @@ LGBM_B200_API int LGBM_BoosterPredictForCSR(BoosterHandle handle, const void* in
                                             const void* data, int data_type, int64_t nindptr, int64_t nelem, int64_t num_col,
                                             int predict_type, int start_iteration, int num_iteration, const char* parameter,
                                             int64_t* out_len, double* out_result);
+/* c_api.h:240-255  (src/c_api.cpp:1320-1350): the listed rows (ascending) of a dataset, with its bin mappers and metadata */
+LGBM_B200_API int LGBM_DatasetGetSubset(const DatasetHandle handle, const int32_t* used_row_indices, int32_t num_used_row_indices,
+                                        const char* parameters, DatasetHandle* out);
 /* c_api.h:344-348  (src/c_api.cpp:1422-1439) field_name: label | weight | group/query | init_score */
 LGBM_B200_API int LGBM_DatasetSetField(DatasetHandle handle, const char* field_name, const void* field_data,
                                        int num_element, int type);

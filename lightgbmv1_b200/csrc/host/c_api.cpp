@@ -234,6 +234,17 @@ int LGBM_DatasetCreateFromCSC(const void* col_ptr, int col_ptr_type, const int32
   API_END();
 }
 
+int LGBM_DatasetGetSubset(const DatasetHandle handle, const int32_t* used_row_indices, int32_t num_used_row_indices,
+                          const char* parameters, DatasetHandle* out) {
+  API_BEGIN();
+  if (!handle || !used_row_indices || !out) Log::Fatal("LGBM_DatasetGetSubset: NULL argument");
+  Config config;
+  config.Set(Config::Str2Map(parameters));
+  if (config.num_threads > 0) omp_set_num_threads(config.num_threads);
+  *out = Dataset::Subset(*reinterpret_cast<const Dataset*>(handle), used_row_indices, num_used_row_indices);
+  API_END();
+}
+
 int LGBM_DatasetSetField(DatasetHandle handle, const char* field_name, const void* field_data, int num_element, int type) {
   API_BEGIN();
   if (!handle || !field_name) Log::Fatal("LGBM_DatasetSetField: NULL argument");
@@ -403,9 +414,35 @@ int LGBM_BoosterPredictForMat(BoosterHandle handle, const void* data, int data_t
   API_BEGIN();
   (void)parameter;
   if (start_iteration != 0) Log::Fatal("start_iteration != 0 is outside this library's path");
-  if (predict_type != C_API_PREDICT_NORMAL && predict_type != C_API_PREDICT_RAW_SCORE)
-    Log::Fatal("predict_type %d is outside this library's path (normal, raw score)", predict_type);
+  if (predict_type != C_API_PREDICT_NORMAL && predict_type != C_API_PREDICT_RAW_SCORE && predict_type != C_API_PREDICT_LEAF_INDEX)
+    Log::Fatal("predict_type %d is outside this library's path (normal, raw score, leaf index)", predict_type);
   Booster* b = reinterpret_cast<Booster*>(handle);
+  if (predict_type == C_API_PREDICT_LEAF_INDEX) {
+    // GBDT::PredictLeafIndex (gbdt_prediction.cpp:77-86): the leaf of every tree, [row][tree]
+    const int n_models_all = b->loaded ? static_cast<int>(b->loaded->trees.size()) : b->gbdt->num_models();
+    const int K = b->loaded ? b->loaded->num_tree_per_iteration : b->gbdt->num_tree_per_iteration();
+    const int want_cols = b->loaded ? b->loaded->max_feature_idx + 1 : b->gbdt->max_feature_idx() + 1;
+    if (ncol != want_cols) Log::Fatal("The number of features in data (%d) is not the same as it was in training data (%d).", ncol, want_cols);
+    int n_models = n_models_all;
+    if (num_iteration > 0) n_models = std::min(n_models, num_iteration * K);
+#pragma omp parallel
+    {
+      std::vector<double> row(ncol);
+#pragma omp for schedule(static)
+      for (int32_t r = 0; r < nrow; ++r) {
+        for (int c = 0; c < ncol; ++c) {
+          const size_t i = is_row_major ? static_cast<size_t>(r) * ncol + c : static_cast<size_t>(c) * nrow + r;
+          row[c] = data_type == 0 ? static_cast<double>(static_cast<const float*>(data)[i]) : static_cast<const double*>(data)[i];
+        }
+        for (int t = 0; t < n_models; ++t) {
+          const Tree& tree = b->loaded ? *b->loaded->trees[t] : b->gbdt->model(t);
+          out_result[static_cast<size_t>(r) * n_models + t] = tree.PredictLeaf(row.data());
+        }
+      }
+    }
+    *out_len = static_cast<int64_t>(nrow) * n_models;
+    return 0;
+  }
   if (b->loaded) {
     const LoadedModel& m = *b->loaded;
     if (ncol != m.max_feature_idx + 1)
@@ -655,10 +692,17 @@ int LGBM_BoosterPredictForCSR(BoosterHandle handle, const void* indptr, int indp
 int LGBM_BoosterCalcNumPredict(BoosterHandle handle, int num_row, int predict_type, int start_iteration, int num_iteration,
                                int64_t* out_len) {
   API_BEGIN();
-  (void)start_iteration; (void)num_iteration;
-  if (predict_type != C_API_PREDICT_NORMAL && predict_type != C_API_PREDICT_RAW_SCORE)
-    Log::Fatal("predict_type %d is outside this library's path (normal, raw score)", predict_type);
+  (void)start_iteration;
+  if (predict_type != C_API_PREDICT_NORMAL && predict_type != C_API_PREDICT_RAW_SCORE && predict_type != C_API_PREDICT_LEAF_INDEX)
+    Log::Fatal("predict_type %d is outside this library's path (normal, raw score, leaf index)", predict_type);
   Booster* b = reinterpret_cast<Booster*>(handle);
+  if (predict_type == C_API_PREDICT_LEAF_INDEX) {
+    const int K = b->loaded ? b->loaded->num_tree_per_iteration : b->gbdt->num_tree_per_iteration();
+    int n_models = b->loaded ? static_cast<int>(b->loaded->trees.size()) : b->gbdt->num_models();
+    if (num_iteration > 0) n_models = std::min(n_models, num_iteration * K);
+    *out_len = static_cast<int64_t>(num_row) * n_models;
+    return 0;
+  }
   *out_len = static_cast<int64_t>(num_row) * (b->loaded ? b->loaded->num_tree_per_iteration : b->gbdt->num_tree_per_iteration());   // one value per row and class
   API_END();
 }

@@ -330,6 +330,40 @@ Dataset* Dataset::FromDenseMatrixAligned(const void* data, int data_type, int32_
   return ds.release();
 }
 
+Dataset* Dataset::Subset(const Dataset& full, const int32_t* idx, int32_t n) {
+  if (n <= 0) Log::Fatal("Check failed: (num_used_row_indices) > (0)");
+  for (int32_t i = 0; i < n; ++i) {
+    if (idx[i] < 0 || idx[i] >= full.num_data_) Log::Fatal("Used indices of subset: element [#%d = %d] outside [0, %d]", i, idx[i], full.num_data_ - 1);
+    if (i > 0 && idx[i] < idx[i - 1]) Log::Fatal("used_row_indices should be sorted in Subset");
+  }
+  std::unique_ptr<Dataset> ds(new Dataset(n));
+  ds->num_total_features_ = full.num_total_features_;
+  ds->mappers_ = full.mappers_;
+  ds->inner_to_real_ = full.inner_to_real_;
+  ds->real_to_inner_ = full.real_to_inner_;
+  ds->bundle_of_ = full.bundle_of_;
+  ds->feature_names_ = full.feature_names_;
+  // the stored values travel as they are (a bundle's overwritten rows included): one row = FS bytes
+  const size_t FS = static_cast<size_t>(std::max(full.num_storage_columns(), 1));
+  const std::vector<uint8_t>& src = full.bins();
+  ds->bins_.resize(static_cast<size_t>(n) * FS);
+#pragma omp parallel for schedule(static)
+  for (int32_t i = 0; i < n; ++i) std::memcpy(ds->bins_.data() + static_cast<size_t>(i) * FS, src.data() + static_cast<size_t>(idx[i]) * FS, FS);
+  ds->bins_pinned_ = lgbcu_pin_host_buffer(ds->bins_.data(), ds->bins_.size()) == 0;
+  // Metadata::Init(fullset, used_indices) (src/io/metadata.cpp:58-125).  (Its query loop runs over the NEW object's
+  // query count, which is still zero there: a subset carries no queries until the caller sets them -- kept.)
+  const Metadata& fm = full.meta_;
+  if (!fm.label.empty()) { ds->meta_.label.resize(n); for (int32_t i = 0; i < n; ++i) ds->meta_.label[i] = fm.label[idx[i]]; }
+  if (!fm.weights.empty()) { ds->meta_.weights.resize(n); for (int32_t i = 0; i < n; ++i) ds->meta_.weights[i] = fm.weights[idx[i]]; }
+  if (!fm.init_score.empty()) {
+    const int K = static_cast<int>(fm.init_score.size() / static_cast<size_t>(full.num_data_));
+    ds->meta_.init_score.resize(static_cast<size_t>(n) * K);
+    for (int k = 0; k < K; ++k)
+      for (int32_t i = 0; i < n; ++i) ds->meta_.init_score[static_cast<size_t>(k) * n + i] = fm.init_score[static_cast<size_t>(k) * full.num_data_ + idx[i]];
+  }
+  return ds.release();
+}
+
 uint32_t Dataset::stored_value(int inner, double v) const {
   const BinMapper& m = *mappers_[inner];
   uint32_t bin = m.ValueToBin(v);

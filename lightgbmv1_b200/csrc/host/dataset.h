@@ -26,6 +26,9 @@ class Dataset {
   // LGBM_DatasetCreateFromMat with reference == nullptr: sample, find bins, bin every row
   static Dataset* FromDenseMatrix(const void* data, int data_type, int32_t nrow, int32_t ncol, bool row_major,
                                   const Config& config);
+  // LGBM_DatasetGetSubset: the listed rows (ascending) of `full` with its mappers, bins and metadata
+  // (Dataset::CopyFeatureMapperFrom + CopySubrow, src/io/dataset.cpp:742-829; Metadata::Init(fullset, indices))
+  static Dataset* Subset(const Dataset& full, const int32_t* used_row_indices, int32_t num_used);
   // ... with a reference dataset: reuse its mappers and feature order (Dataset::CreateValid)
   static Dataset* FromDenseMatrixAligned(const void* data, int data_type, int32_t nrow, int32_t ncol, bool row_major,
                                          const Dataset& reference, const Config& config);

@@ -31,6 +31,8 @@ class GBDT {
   bool TrainOneIter(const float* grad, const float* hess);  // true = finished (cannot split any more)
   int current_iteration() const { return static_cast<int>(models_.size()) / num_tree_per_iteration_; }   // GBDT::GetCurrentIteration
   int num_models() const { return static_cast<int>(models_.size()); }
+  const Tree& model(int i) const { return *models_[i]; }
+  int max_feature_idx() const { return train_->num_total_features() - 1; }
   int num_tree_per_iteration() const { return num_tree_per_iteration_; }
   int num_data() const { return train_->num_data(); }
   void GetTrainScore(double* out, bool converted) const;      // LGBM_BoosterGetPredict(data_idx = 0)

@@ -181,8 +181,10 @@ Tree* Tree::FromString(const std::string& text) {
 }
 
 // Tree::Predict -> GetLeaf -> NumericalDecision (include/LightGBM/tree.h:250-283)
-double Tree::Predict(const double* x) const {
-  if (num_leaves_ <= 1) return leaf_value_[0];
+double Tree::Predict(const double* x) const { return leaf_value_[PredictLeaf(x)]; }
+
+int Tree::PredictLeaf(const double* x) const {
+  if (num_leaves_ <= 1) return 0;
   int node = 0;
   while (node >= 0) {
     double fval = x[split_feature_[node]];
@@ -210,7 +212,7 @@ double Tree::Predict(const double* x) const {
       node = fval <= threshold_[node] ? left_child_[node] : right_child_[node];
     }
   }
-  return leaf_value_[~node];
+  return ~node;
 }
 
 }  // namespace lgb

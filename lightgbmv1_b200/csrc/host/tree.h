@@ -31,6 +31,7 @@ class Tree {
   // good for Predict / ToString (bin-space thresholds are not part of the text)
   static Tree* FromString(const std::string& text);
   double Predict(const double* features) const;  // raw feature values (Tree::Predict / NumericalDecision)
+  int PredictLeaf(const double* features) const;  // Tree::PredictLeafIndex (tree.h:420-432)
 
   int num_leaves() const { return num_leaves_; }
   double leaf_value(int i) const { return leaf_value_[i]; }

@@ -219,3 +219,27 @@ def test_model_does_not_depend_on_the_lookahead(lookahead, monkeypatch):
     monkeypatch.setenv("LGBCU_LOOKAHEAD", lookahead)
     ref, ours, br, bo, nr, no = run_both(X, y, params, 5)
     assert_same_model(ref, ours, br, bo)
+
+
+def test_training_on_a_row_subset():
+    """LGBM_DatasetGetSubset (python's Dataset.subset / lgb.cv folds): both libraries train on the same rows of the same
+    parent dataset -- the parent's bin mappers, the subset's labels and weights -- and give the same trees"""
+    import ctypes as C
+    X, y = higgs_like(51, 40_000)
+    w = (np.random.default_rng(52).random(len(y)) + 0.5).astype(np.float32)
+    idx = np.sort(np.random.default_rng(53).choice(len(y), size=26_000, replace=False)).astype(np.int32)
+    params = "objective=binary num_leaves=31 min_data_in_leaf=20 verbosity=-1"
+    out = {}
+    for name, lib, extra in (("ref", capi.reference(), REF_EXTRA), ("ours", capi.ours(), "")):
+        ds = lib.dataset_from_mat(X, params + extra)
+        lib.set_field(ds, "label", y); lib.set_field(ds, "weight", w)
+        sub = C.c_void_p()
+        lib.check(lib.lib.LGBM_DatasetGetSubset(ds, idx.ctypes.data_as(C.POINTER(C.c_int32)), C.c_int32(len(idx)),
+                                                C.c_char_p((params + extra).encode()), C.byref(sub)))
+        b = lib.booster_create(sub, params + extra)
+        for _ in range(8):
+            lib.update(b)
+        out[name] = (lib, b)
+    (ref, br), (ours, bo) = out["ref"], out["ours"]
+    assert_same_model(ref, ours, br, bo)
+    assert np.max(np.abs(ref.get_predict(br, len(idx)) - ours.get_predict(bo, len(idx)))) <= 1e-9

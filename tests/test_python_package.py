@@ -20,7 +20,8 @@ PKG = os.environ.get("LGBM_REF_PYTHON_PACKAGE", "/root/reference/python-package"
 def _train_path_symbols():
     """LGBM_* names used by the functions lgb.train(params, lgb.Dataset(X, y)) executes (found by tracing the package
     on the reference library once; kept as a list so that the check needs no reference tree)."""
-    return ["LGBM_GetLastError", "LGBM_RegisterLogCallback", "LGBM_DatasetCreateFromMat", "LGBM_DatasetSetField", "LGBM_DatasetGetField",
+    return ["LGBM_GetLastError", "LGBM_RegisterLogCallback", "LGBM_DatasetCreateFromMat", "LGBM_DatasetCreateFromCSR", "LGBM_DatasetCreateFromCSC",
+            "LGBM_DatasetGetSubset", "LGBM_BoosterPredictForCSR", "LGBM_DatasetSetField", "LGBM_DatasetGetField",
             "LGBM_DatasetSetFeatureNames", "LGBM_DatasetGetFeatureNames", "LGBM_DatasetUpdateParamChecking",
             "LGBM_DatasetGetNumData", "LGBM_DatasetGetNumFeature", "LGBM_DatasetFree", "LGBM_BoosterCreate",
             "LGBM_BoosterFree", "LGBM_BoosterAddValidData", "LGBM_BoosterGetNumClasses", "LGBM_BoosterGetEvalCounts",
@@ -132,3 +133,53 @@ def test_loaded_multiclass_model_predicts_like_the_reference_cpu():
     ours.check(ours.lib.LGBM_BoosterGetNumClasses(bo, C.byref(k))); assert k.value == 3
     ours.check(ours.lib.LGBM_BoosterGetCurrentIteration(bo, C.byref(k))); assert k.value == 5
     assert ours.model_string(bo) == text
+
+
+def test_subset_and_leaf_index_prediction_cpu():
+    """LGBM_DatasetGetSubset (python's Dataset.subset / lgb.cv) and predict_type = leaf index on a loaded model: CPU-only
+    checks against the reference -- the subset's bins equal the reference's subset's, the leaf indices equal its."""
+    if not (H.have_ref() and os.path.exists(H.REF_SHIM_SO)):
+        pytest.skip("oracle/_ref not built")
+    os.environ["LGBM_B200_HOST_BINNING"] = "1"
+    try:
+        C.CDLL(H.REF_SO, mode=C.RTLD_GLOBAL); shim = C.CDLL(H.REF_SHIM_SO)
+        rng = np.random.default_rng(8)
+        X = rng.standard_normal((5000, 9)); X[::7, 3] = np.nan; X[:, 5] = rng.integers(0, 6, size=5000)
+        y = (np.nan_to_num(X[:, 0]) + X[:, 1] ** 2 > 1).astype(np.float32)
+        w = (rng.random(5000) + 0.5).astype(np.float32)
+        idx = np.sort(rng.choice(5000, size=1700, replace=False)).astype(np.int32)
+        ref, ours = capi.reference(), capi.ours()
+        p = "max_bin=63 categorical_feature=5 verbosity=-1"
+        subs = {}
+        for name, lib in (("ref", ref), ("ours", ours)):
+            ds = lib.dataset_from_mat(X, p)
+            lib.set_field(ds, "label", y); lib.set_field(ds, "weight", w)
+            sub = C.c_void_p()
+            lib.check(lib.lib.LGBM_DatasetGetSubset(ds, idx.ctypes.data_as(C.POINTER(C.c_int32)), C.c_int32(len(idx)), C.c_char_p(p.encode()), C.byref(sub)))
+            n = C.c_int(); lib.check(lib.lib.LGBM_DatasetGetNumData(sub, C.byref(n))); assert n.value == len(idx)
+            subs[name] = sub
+        nf = shim.ref_num_inner_features(subs["ref"])
+        bins = np.empty((len(idx), nf), dtype=np.int32); real = np.empty(nf, dtype=np.int32)
+        ours.check(ours.lib.LGBM_B200_DatasetDumpBins(subs["ours"], bins.ctypes.data_as(C.POINTER(C.c_int32)), real.ctypes.data_as(C.POINTER(C.c_int32))))
+        for f in range(nf):
+            want = np.empty(len(idx), dtype=np.int32)
+            shim.ref_feature_bin_column(subs["ref"], C.c_int(f), want.ctypes.data_as(C.POINTER(C.c_int32)))
+            assert np.array_equal(bins[:, f], want), f"inner feature {f}: subset bins differ"
+        # the subset's label came along
+        out_len = C.c_int(); out_ptr = C.c_void_p(); out_type = C.c_int()
+        ours.check(ours.lib.LGBM_DatasetGetField(subs["ours"], C.c_char_p(b"label"), C.byref(out_len), C.byref(out_ptr), C.byref(out_type)))
+        got = np.ctypeslib.as_array(C.cast(out_ptr, C.POINTER(C.c_float)), shape=(out_len.value,))
+        assert np.array_equal(got, y[idx])
+        # leaf indices from a model the reference trained
+        _, br, _ = capi.train(ref, X, y, "objective=binary num_leaves=15 categorical_feature=5 verbosity=-1 num_threads=2", 5)
+        bo = ours.load_model_from_string(ref.model_string(br))
+        def leaves(lib, b):
+            out = np.empty(len(X) * 5, dtype=np.float64); n = C.c_int64()
+            lib.check(lib.lib.LGBM_BoosterPredictForMat(b, X.ctypes.data_as(C.c_void_p), C.c_int(1), C.c_int32(X.shape[0]), C.c_int32(X.shape[1]),
+                                                        C.c_int(1), C.c_int(2), C.c_int(0), C.c_int(-1), C.c_char_p(b""), C.byref(n),
+                                                        out.ctypes.data_as(C.POINTER(C.c_double))))
+            assert n.value == len(out)
+            return out
+        assert np.array_equal(leaves(ref, br), leaves(ours, bo))
+    finally:
+        os.environ.pop("LGBM_B200_HOST_BINNING", None)
