@@ -381,16 +381,18 @@ __global__ void __cluster_dims__(HIST_CLUSTER, 1, 1) __launch_bounds__(HIST_THRE
 // more slots than fit, take the global-atomic path (hist_global_wide_path).  Measured at 2M x 28, max_bin = 1023:
 // 2.5 ms of histogram time per iteration against 10.2 ms with global atomics alone (the 8-bit kernel: 0.74 ms at 255 bins).
 #define WIDE_HIST_MIN_ELEMS 32768   /* rows x features below which a leaf goes straight to global atomics */
-__device__ __forceinline__ void wide_add64(unsigned* w, i64 v) {   // w[0] low word, w[1] high word
+__device__ __forceinline__ void wide_add64(unsigned* lo_word, unsigned* hi_word, i64 v) {
   const unsigned lo = (unsigned)v;
-  const unsigned old = atomicAdd(&w[0], lo);
+  const unsigned old = atomicAdd(lo_word, lo);
   const unsigned carry = (old + lo) < old ? 1u : 0u;
   const unsigned hi = (unsigned)((unsigned long long)v >> 32) + carry;
-  if (hi) atomicAdd(&w[1], hi);
+  if (hi) atomicAdd(hi_word, hi);
 }
 
 __global__ void __launch_bounds__(256) k_hist_wide(DevView V, int leaf_arg, int smem_slots) {
-  extern __shared__ __align__(16) unsigned wide_smem[];   // [slots][4]: g low, g high, h low, h high
+  // four planes of one word per slot -- g low, g high, h low, h high -- so that the lanes of one atomic instruction, which
+  // hit random slots, spread over all 32 banks (slot-major [slot][4] words put every low word on one of 8 banks)
+  extern __shared__ __align__(16) unsigned wide_smem[];
   STAMP(V.ctl, 0);
   DevLeaf L; bool is_root; int bid, nblocks;
   if (!hist_pick_work(V, leaf_arg, 1, &L, &is_root, &bid, &nblocks)) return;
@@ -420,19 +422,21 @@ __global__ void __launch_bounds__(256) k_hist_wide(DevView V, int leaf_arg, int 
         }
         continue;
       }
-      for (int i = tid; i < Ft.nslots * 4; i += blockDim.x) wide_smem[i] = 0u;
+      const int ns = Ft.nslots;
+      unsigned* g_lo = wide_smem; unsigned* g_hi = wide_smem + ns; unsigned* h_lo = wide_smem + 2 * ns; unsigned* h_hi = wide_smem + 3 * ns;
+      for (int i = tid; i < ns * 4; i += blockDim.x) wide_smem[i] = 0u;
       __syncthreads();
       for (int p = r0 + tid; p < r1; p += blockDim.x) {
         const int row = identity ? p : idx[p];
         int b = col[row]; if (Ft.wide) b |= (int)col[row + V.col_stride] << 8;
         const float2 gh = V.gh[row];
-        wide_add64(&wide_smem[b * 4], to_fixed(gh.x, scale_g));
-        wide_add64(&wide_smem[b * 4 + 2], to_fixed(gh.y, scale_h));
+        wide_add64(&g_lo[b], &g_hi[b], to_fixed(gh.x, scale_g));
+        wide_add64(&h_lo[b], &h_hi[b], to_fixed(gh.y, scale_h));
       }
       __syncthreads();
-      for (int b = tid; b < Ft.nslots; b += blockDim.x) {
-        const i64 g = (i64)(((unsigned long long)wide_smem[b * 4 + 1] << 32) | wide_smem[b * 4]);
-        const i64 h = (i64)(((unsigned long long)wide_smem[b * 4 + 3] << 32) | wide_smem[b * 4 + 2]);
+      for (int b = tid; b < ns; b += blockDim.x) {
+        const i64 g = (i64)(((unsigned long long)g_hi[b] << 32) | g_lo[b]);
+        const i64 h = (i64)(((unsigned long long)h_hi[b] << 32) | h_lo[b]);
         if (g) atomic_add_i64(&out[b].g, g);
         if (h) atomic_add_i64(&out[b].h, h);
       }
