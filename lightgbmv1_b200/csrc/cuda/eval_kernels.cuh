@@ -39,7 +39,8 @@ __global__ void __launch_bounds__(EVAL_THREADS) k_eval_pointwise(int n, int kind
   __shared__ double s_warp[EVAL_THREADS / 32];
   double acc = 0.0;
   for (int i = blockIdx.x * blockDim.x + threadIdx.x; i < n; i += gridDim.x * blockDim.x) {
-    const double s = score[i];
+    double s = score[i];
+    if (conv_exp == 2) s = (double)((s > 0.0) - (s < 0.0)) * s * s;   // RegressionL2loss::ConvertOutput with reg_sqrt
     const float y = label[i];
     double loss;
     if (kind == 0) {
@@ -53,7 +54,7 @@ __global__ void __launch_bounds__(EVAL_THREADS) k_eval_pointwise(int n, int kind
       const double x = fabs(s - y);
       loss = sigmoid * x - sigmoid * sigmoid * log(1.0f + x / sigmoid);
     } else if (kind == 6) {          // PoissonMetric::LossOnPoint (:229-235); conv_exp: the objective's exp first
-      double t = conv_exp ? exp(s) : s;
+      double t = conv_exp == 1 ? exp(s) : s;
       const double eps = 1e-10f;
       if (t < eps) t = eps;
       loss = t - y * log(t);
@@ -71,7 +72,7 @@ __global__ void __launch_bounds__(EVAL_THREADS) k_eval_pointwise(int n, int kind
       acc += -(a + b);
       continue;
     } else if (kind == 13) {         // GammaDevianceMetric::LossOnPoint (regression_metric.hpp:284-288)
-      const double t = conv_exp ? exp(s) : s;
+      const double t = conv_exp == 1 ? exp(s) : s;
       const double tmp = y / (t + 1.0e-9);
       loss = tmp - safe_log(tmp) - 1;
     } else if (kind == 11) {         // MAPEMetric::LossOnPoint (regression_metric.hpp:248-250)
@@ -84,7 +85,7 @@ __global__ void __launch_bounds__(EVAL_THREADS) k_eval_pointwise(int n, int kind
       b *= 1.0f - prob > log_arg_epsilon ? log(1.0f - prob) : log(log_arg_epsilon);
       loss = -(a + b);
     } else if (kind == 7) {          // GammaMetric::LossOnPoint (:261-268), written out as there (psi = 1)
-      const double t = conv_exp ? exp(s) : s;
+      const double t = conv_exp == 1 ? exp(s) : s;
       const double psi = 1.0;
       const double theta = -1.0 / t;
       const double a = psi;
@@ -92,7 +93,7 @@ __global__ void __launch_bounds__(EVAL_THREADS) k_eval_pointwise(int n, int kind
       const double c = 1. / psi * safe_log(y / psi) - safe_log(y) - 0;
       loss = -((y * theta - b) / a + c);
     } else if (kind == 8) {          // TweedieMetric::LossOnPoint (:305-314); `sigmoid` carries tweedie_variance_power
-      double t = conv_exp ? exp(s) : s;
+      double t = conv_exp == 1 ? exp(s) : s;
       const double eps = 1e-10f;
       if (t < eps) t = eps;
       const double a = y * exp((1 - sigmoid) * log(t)) / (1 - sigmoid);

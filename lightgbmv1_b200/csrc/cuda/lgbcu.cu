@@ -1013,7 +1013,7 @@ int lgbcu_get_gradients(LgbCuContext* c) {
   if (c->objective == LGBCU_OBJ_BINARY) {
     LAUNCH(k_grad_binary, g, 256, 0, c->stream, c->N, c->d_score, c->d_label, w, c->obj_p[0], c->obj_p[1], c->obj_p[2], c->d_grad, c->d_hess);
   } else if (c->objective == LGBCU_OBJ_L2) {
-    LAUNCH(k_grad_l2, g, 256, 0, c->stream, c->N, c->d_score, c->d_label, w, c->d_grad, c->d_hess);
+    LAUNCH(k_grad_l2, g, 256, 0, c->stream, c->N, c->d_score, c->d_label, w, c->d_grad, c->d_hess, c->obj_p[0] != 0.0 ? 1 : 0);
   } else if (c->objective == LGBCU_OBJ_LAMBDARANK) {
     if (rank_prepare(c)) return -1;
     if (rank_launch(c)) return -1;

@@ -27,13 +27,15 @@ __global__ void k_grad_binary(int n, const double* __restrict__ score, const flo
 
 // RegressionL2loss::GetGradients (src/objective/regression_objective.hpp:125-140)
 __global__ void k_grad_l2(int n, const double* __restrict__ score, const float* __restrict__ label,
-                          const float* __restrict__ weight, float* __restrict__ grad, float* __restrict__ hess) {
+                          const float* __restrict__ weight, float* __restrict__ grad, float* __restrict__ hess, int sqrt_label) {
   for (int i = blockIdx.x * blockDim.x + threadIdx.x; i < n; i += gridDim.x * blockDim.x) {
+    // reg_sqrt: the objective sees sign(label) * sqrt(|label|) (RegressionL2loss::Init, :110-118; float arithmetic there)
+    const float lab = sqrt_label ? (float)((label[i] > 0.0f) - (label[i] < 0.0f)) * sqrtf(fabsf(label[i])) : label[i];
     if (weight == nullptr) {
-      grad[i] = (float)(score[i] - label[i]);
+      grad[i] = (float)(score[i] - lab);
       hess[i] = 1.0f;
     } else {
-      grad[i] = (float)((score[i] - label[i]) * weight[i]);
+      grad[i] = (float)((score[i] - lab) * weight[i]);
       hess[i] = (float)(weight[i]);
     }
   }

@@ -314,7 +314,8 @@ int lgbcu_eval(LgbCuContext* c, int32_t set, int32_t kind, double sigmoid, doubl
                  kind == LGBCU_METRIC_GAMMA ? 7 : kind == LGBCU_METRIC_TWEEDIE ? 8 : kind == LGBCU_METRIC_BINARY_ERROR ? 9 :
                  kind == LGBCU_METRIC_XENTROPY ? 10 : kind == LGBCU_METRIC_MAPE ? 11 : kind == LGBCU_METRIC_XENTLAMBDA ? 12 : kind == LGBCU_METRIC_GAMMA_DEVIANCE ? 13 : 0;
   // metrics see the objective's ConvertOutput: exp for the log-link objectives
-  const int conv_exp = (c->objective == LGBCU_OBJ_POISSON || c->objective == LGBCU_OBJ_GAMMA || c->objective == LGBCU_OBJ_TWEEDIE) ? 1 : 0;
+  const int conv_exp = (c->objective == LGBCU_OBJ_POISSON || c->objective == LGBCU_OBJ_GAMMA || c->objective == LGBCU_OBJ_TWEEDIE) ? 1 :
+                       (c->objective == LGBCU_OBJ_L2 && c->obj_p[0] != 0.0) ? 2 : 0;   // 2: the reg_sqrt objective squares its output
   LAUNCH(k_eval_pointwise, grid, EVAL_THREADS, 0, c->stream, n, pk, sigmoid, conv_exp, score,
          label, weight, c->d_eval_partial);
   LAUNCH(k_eval_final, 1, EVAL_THREADS, 0, c->stream, grid, 1, c->d_eval_partial, c->d_eval_out);

@@ -36,6 +36,7 @@ struct LoadedModel {
   bool exp_out = false;    // the log-link regressions (poisson, gamma, tweedie): predictions are exp(raw)
   bool softplus_out = false;   // cross_entropy_lambda: predictions are log(1 + exp(raw))
   bool average_output = false; // boosting=rf: the header's "average_output" line
+  bool square_out = false;     // "regression sqrt": predictions are sign(raw) * raw^2
   int num_tree_per_iteration = 1;   // multiclass: trees (and outputs per row) per iteration
   bool softmax = false;             // "multiclass ...": predictions are the softmax of a row's raw scores
   double ova_sigmoid = 0.0;         // "multiclassova ...": > 0, a sigmoid per class
@@ -91,6 +92,7 @@ LoadedModel* ParseModel(const std::string& text) {
   }
   if (m->objective.rfind("cross_entropy", 0) == 0 && m->objective.rfind("cross_entropy_lambda", 0) != 0) m->sigmoid = 1.0;
   if (m->objective.rfind("cross_entropy_lambda", 0) == 0) m->softplus_out = true;
+  if (m->objective.rfind("regression", 0) == 0 && m->objective.find(" sqrt") != std::string::npos) m->square_out = true;
   if (m->objective.rfind("poisson", 0) == 0 || m->objective.rfind("gamma", 0) == 0 || m->objective.rfind("tweedie", 0) == 0) m->exp_out = true;
   // trees: "Tree=i" ... blank line, until "end of trees"
   std::string cur;
@@ -465,6 +467,7 @@ int LGBM_BoosterPredictForMat(BoosterHandle handle, const void* data, int data_t
         if (!raw && m.average_output && n_iter > 0) for (int k = 0; k < K; ++k) sc[k] /= n_iter;
         if (!raw && m.sigmoid > 0) sc[0] = 1.0f / (1.0f + std::exp(-m.sigmoid * sc[0]));
         if (!raw && m.exp_out) sc[0] = std::exp(sc[0]);
+        if (!raw && m.square_out) sc[0] = ((sc[0] > 0.0) - (sc[0] < 0.0)) * sc[0] * sc[0];
         if (!raw && m.softplus_out) sc[0] = std::log(1.0f + std::exp(sc[0]));
         if (!raw && m.ova_sigmoid > 0) for (int k = 0; k < K; ++k) sc[k] = 1.0f / (1.0f + std::exp(-m.ova_sigmoid * sc[k]));
         if (!raw && m.softmax) {   // Common::Softmax

@@ -81,14 +81,20 @@ class BinaryLogloss : public Objective {
 // src/objective/regression_objective.hpp (RegressionL2loss)
 class RegressionL2 : public Objective {
  public:
-  explicit RegressionL2(const Config& c) {
-    if (c.reg_sqrt) Log::Fatal("reg_sqrt is outside this library's path");
-  }
+  explicit RegressionL2(const Config& c) : sqrt_(c.reg_sqrt) {}
   void Init(const Metadata& meta, data_size_t n, const SumSync&) override {
     num_data_ = n; label_ = meta.label.data(); weights_ = meta.weights.empty() ? nullptr : meta.weights.data();
     if (meta.label.empty()) Log::Fatal("Label should not be NULL");
+    if (sqrt_) {   // regression_objective.hpp:110-118 (the device's gradient kernel applies the same transform)
+      trans_label_.resize(n);
+      for (data_size_t i = 0; i < n; ++i) trans_label_[i] = ((label_[i] > 0.0f) - (label_[i] < 0.0f)) * std::sqrt(std::fabs(label_[i]));
+      label_ = trans_label_.data();
+    }
   }
-  void Configure(LgbCuContext* ctx) const override { Check(lgbcu_set_objective(ctx, LGBCU_OBJ_L2, 0, 0, 0)); }
+  void Configure(LgbCuContext* ctx) const override { Check(lgbcu_set_objective(ctx, LGBCU_OBJ_L2, sqrt_ ? 1 : 0, 0, 0)); }
+  void ConvertOutput(const double* in, double* out) const override {
+    out[0] = sqrt_ ? ((in[0] > 0.0) - (in[0] < 0.0)) * in[0] * in[0] : in[0];
+  }
   double BoostFromScore(int) const override {
     double suml = 0.0f, sumw = 0.0f;
     if (weights_) {  // (OpenMP reductions as in regression_objective.hpp BoostFromScore)
@@ -102,10 +108,12 @@ class RegressionL2 : public Objective {
     return suml / sumw;
   }
   bool IsConstantHessian() const override { return weights_ == nullptr; }
-  std::string ToString() const override { return "regression"; }
+  std::string ToString() const override { return sqrt_ ? "regression sqrt" : "regression"; }
   const char* Name() const override { return "regression"; }
 
  private:
+  bool sqrt_;
+  std::vector<label_t> trans_label_;
   data_size_t num_data_ = 0; const label_t* label_ = nullptr; const label_t* weights_ = nullptr;
 };
 

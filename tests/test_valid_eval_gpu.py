@@ -162,6 +162,24 @@ def test_rank_xendcg_identical_run(weighted):
     _compare(ref, ours, rtol=1e-7)
 
 
+@pytest.mark.parametrize("weighted", [False, True])
+def test_reg_sqrt_objective_and_converted_metrics(weighted):
+    """reg_sqrt (RegressionL2loss, regression_objective.hpp:96-160): the objective fits sign(y) sqrt(|y|), predictions and
+    metrics see sign(s) s^2"""
+    rng = np.random.default_rng(34)
+    def make(n):
+        X = rng.standard_normal((n, 8)).astype(np.float32)
+        y = ((2 * X[:, 0] + X[:, 1] * X[:, 2]) ** 3 + rng.standard_normal(n)).astype(np.float32)
+        return X, y
+    Xt, yt = make(20_000); Xv, yv = make(6_000)
+    wt = (rng.random(len(yt)) + 0.5).astype(np.float32) if weighted else None
+    wv = (rng.random(len(yv)) + 0.5).astype(np.float32) if weighted else None
+    params = "objective=regression reg_sqrt=true metric=l2,l1,rmse num_leaves=15 min_data_in_leaf=20 learning_rate=0.1 verbosity=-1"
+    ref = _run(capi.reference(), Xt, yt, Xv, yv, params, 6, wt, wv, extra=REF_EXTRA)
+    ours = _run(capi.ours(), Xt, yt, Xv, yv, params, 6, wt, wv)
+    _compare(ref, ours)
+
+
 def test_gamma_deviance_metric():
     rng = np.random.default_rng(15)
     def make(n):
