@@ -16,6 +16,7 @@
 #include <LightGBM/objective_function.h>
 #include <LightGBM/tree.h>
 #include <LightGBM/tree_learner.h>
+#include <LightGBM/utils/common.h>
 #include <LightGBM/utils/log.h>
 
 #include <cstring>
@@ -53,11 +54,13 @@ class CudaB200TreeLearner : public TreeLearner {
       for (data_size_t i = 0; i < num_data_; ++i) cols[f][i] = static_cast<uint8_t>(it->RawGet(i));
       ptrs[f] = cols[f].data();
       const BinMapper* m = train_data->FeatureBinMapper(f);
-      if (m->num_bin() + (m->GetMostFreqBin() == 0 ? 0 : 1) > 256 || m->bin_type() != BinType::NumericalBin)
-        Log::Fatal("CudaB200TreeLearner: feature %d needs more than 8-bit numerical bins", f);
+      if (m->num_bin() + (m->GetMostFreqBin() == 0 ? 0 : 1) > 256)
+        Log::Fatal("CudaB200TreeLearner: feature %d needs more than 8-bit bins (this shim hands over byte columns)", f);
+      has_categorical_ = has_categorical_ || m->bin_type() == BinType::CategoricalBin;
       meta[f].num_bin = m->num_bin(); meta[f].most_freq_bin = static_cast<int>(m->GetMostFreqBin());
       meta[f].default_bin = static_cast<int>(m->GetDefaultBin()); meta[f].missing_type = static_cast<int>(m->missing_type());
-      meta[f].real_index = train_data->RealFeatureIndex(f); meta[f].bin_type = LGBCU_BIN_NUMERICAL; meta[f].penalty = 1.0;
+      meta[f].real_index = train_data->RealFeatureIndex(f);
+      meta[f].bin_type = m->bin_type() == BinType::CategoricalBin ? LGBCU_BIN_CATEGORICAL : LGBCU_BIN_NUMERICAL; meta[f].penalty = 1.0;
     }
     Need(lgbcu_set_dataset_columns(ctx_, num_data_, F, ptrs.data(), meta.data()));
     PushParams();
@@ -75,9 +78,31 @@ class CudaB200TreeLearner : public TreeLearner {
     int n = 0;
     Need(lgbcu_train_tree(ctx_, records_.data(), &n));
     std::unique_ptr<Tree> tree(new Tree(config_->num_leaves, false));
+    std::vector<uint32_t> cat_sets;   // the tree's categorical bin sets (8 words each)
+    if (has_categorical_) {
+      int32_t nsets = 0;
+      Need(lgbcu_tree_cat_sets(ctx_, nullptr, 0, &nsets));
+      if (nsets > 0) { cat_sets.resize(static_cast<size_t>(nsets) * 8); Need(lgbcu_tree_cat_sets(ctx_, cat_sets.data(), nsets, &nsets)); }
+    }
     for (int i = 0; i < n; ++i) {
       const LgbCuSplitRecord& r = records_[i];
       const BinMapper* m = train_data_->FeatureBinMapper(r.feature);
+      if (m->bin_type() == BinType::CategoricalBin) {   // SerialTreeLearner::SplitInner, categorical branch (:592-621)
+        const uint32_t* set = cat_sets.data() + static_cast<size_t>(r.threshold) * 8;
+        std::vector<uint32_t> bins;
+        std::vector<int> cats;
+        for (int b = 0; b < m->num_bin(); ++b) {
+          if (!((set[b >> 5] >> (b & 31)) & 1u)) continue;
+          bins.push_back(static_cast<uint32_t>(b));
+          cats.push_back(static_cast<int>(train_data_->RealThreshold(r.feature, static_cast<uint32_t>(b))));
+        }
+        const std::vector<uint32_t> inner = Common::ConstructBitset(bins.data(), static_cast<int>(bins.size()));
+        const std::vector<uint32_t> outer = Common::ConstructBitset(cats.data(), static_cast<int>(cats.size()));
+        tree->SplitCategorical(r.leaf, r.feature, r.real_feature, inner.data(), static_cast<int>(inner.size()), outer.data(),
+                               static_cast<int>(outer.size()), r.left_output, r.right_output, r.left_count, r.right_count,
+                               r.left_sum_hessian, r.right_sum_hessian, static_cast<float>(r.gain), m->missing_type());
+        continue;
+      }
       tree->Split(r.leaf, r.feature, r.real_feature, static_cast<uint32_t>(r.threshold),
                   train_data_->RealThreshold(r.feature, static_cast<uint32_t>(r.threshold)), r.left_output, r.right_output,
                   r.left_count, r.right_count, r.left_sum_hessian, r.right_sum_hessian, static_cast<float>(r.gain),
@@ -122,6 +147,15 @@ class CudaB200TreeLearner : public TreeLearner {
     p.lambda_l2 = config_->lambda_l2; p.min_gain_to_split = config_->min_gain_to_split;
     p.max_delta_step = config_->max_delta_step; p.path_smooth = config_->path_smooth;
     Need(lgbcu_set_tree_params(ctx_, &p));
+    if (has_categorical_)
+      Need(lgbcu_set_cat_params(ctx_, config_->cat_smooth, config_->cat_l2, config_->max_cat_threshold, config_->min_data_per_group,
+                                config_->max_cat_to_onehot));
+    if (!config_->monotone_constraints.empty()) {   // FeatureMetainfo::monotone_type (feature_histogram.hpp:1131-1138)
+      const int F = train_data_->num_features();
+      std::vector<int8_t> types(F);
+      for (int f = 0; f < F; ++f) types[f] = config_->monotone_constraints[train_data_->RealFeatureIndex(f)];
+      Need(lgbcu_set_monotone(ctx_, types.data(), F, config_->monotone_penalty));
+    }
   }
   const Config* config_;
   const Dataset* train_data_ = nullptr;
@@ -129,6 +163,7 @@ class CudaB200TreeLearner : public TreeLearner {
   LgbCuContext* ctx_ = nullptr;
   std::vector<LgbCuSplitRecord> records_;
   const data_size_t* bag_ = nullptr; data_size_t bag_cnt_ = 0;
+  bool has_categorical_ = false;
 };
 
 class GBDTWithB200Learner : public GBDT {

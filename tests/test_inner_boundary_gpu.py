@@ -51,3 +51,33 @@ def test_reference_gbdt_around_the_b200_tree_learner_gives_the_stock_model(param
     hs, hw = capi.header_lines(stock), capi.header_lines(swapped)
     for k in ("version", "num_class", "max_feature_idx", "objective", "feature_names", "feature_infos"):
         assert hs.get(k) == hw.get(k), k
+
+
+@pytest.mark.parametrize("kind", ["categorical", "monotone"])
+def test_categorical_and_monotone_through_the_reference_tree_learner_interface(kind):
+    """The same swap for the F4 paths: categorical splits reach the reference's Tree::SplitCategorical from the device's
+    bin sets, monotone constraints go to the device from the reference's Config"""
+    from test_oracle_vs_reference import categorical_matrix
+    from test_categorical_gpu import target
+    n, iters = 25_000, 6
+    ref = capi.reference()
+    if kind == "categorical":
+        X = categorical_matrix(21, n)
+        z = target(X, np.random.default_rng(22))
+        y = (z > np.median(z)).astype(np.float32)
+        p = "objective=binary num_leaves=31 min_data_in_leaf=20 categorical_feature=2,4,5 enable_bundle=false verbosity=-1" + REF_EXTRA
+    else:
+        X, _ = higgs_like(23, n, F=8)
+        y = (1.5 * X[:, 0] - X[:, 1] + 0.5 * X[:, 1] * X[:, 2] + 0.5 * np.random.default_rng(24).standard_normal(n)).astype(np.float32)
+        p = "objective=regression num_leaves=31 min_data_in_leaf=20 monotone_constraints=1,-1,0,0,0,0,0,0 monotone_penalty=0.5 verbosity=-1" + REF_EXTRA
+    ds = ref.dataset_from_mat(X, p)
+    ref.set_field(ds, "label", y)
+    b = ref.booster_create(ds, p)
+    for _ in range(iters):
+        ref.update(b)
+    stock = ref.model_string(b)
+    swapped = shim_train(ds, p, iters)
+    same, n_trees, first = capi.compare_models(stock, swapped, rtol_value=H.VALUE_RTOL)
+    assert n_trees == iters and same == n_trees, f"{same}/{n_trees} trees identical; first mismatch: {first}"
+    if kind == "categorical":
+        assert any(int(t["num_cat"][0]) > 0 for t in capi.parse_trees(swapped))
