@@ -183,3 +183,23 @@ def test_subset_and_leaf_index_prediction_cpu():
         assert np.array_equal(leaves(ref, br), leaves(ours, bo))
     finally:
         os.environ.pop("LGBM_B200_HOST_BINNING", None)
+
+
+def test_dataset_parameter_errors_cpu():
+    """Dataset-level parameters are checked where the reference checks them (no device needed to build a Dataset)"""
+    ours = capi.ours()
+    X = np.random.default_rng(1).standard_normal((500, 4))
+    with pytest.raises(capi.LGBMError, match="max_bin_by_feature"):
+        ours.dataset_from_mat(X, "max_bin_by_feature=10,20 verbosity=-1")            # one entry per column is needed
+    with pytest.raises(capi.LGBMError, match="max_bin_by_feature"):
+        ours.dataset_from_mat(X, "max_bin_by_feature=10,20,1,5 verbosity=-1")        # every entry > 1
+    with pytest.raises(capi.LGBMError, match="column name"):
+        ours.dataset_from_mat(X, "categorical_feature=name:a,b verbosity=-1")        # names need a file header
+    with pytest.raises(capi.LGBMError, match="max_bin"):
+        ours.dataset_from_mat(X, "max_bin=70000 verbosity=-1")
+    ds = ours.dataset_from_mat(np.floor(np.abs(X) * 3), "categorical_feature=0,2 max_bin_by_feature=4,8,16,32 verbosity=-1")
+    n = C.c_int(); ours.check(ours.lib.LGBM_DatasetGetNumFeature(ds, C.byref(n))); assert n.value == 4
+    sub = C.c_void_p()
+    bad = np.array([3, 2, 1], dtype=np.int32)
+    with pytest.raises(capi.LGBMError, match="sorted"):
+        ours.check(ours.lib.LGBM_DatasetGetSubset(ds, bad.ctypes.data_as(C.POINTER(C.c_int32)), C.c_int32(3), C.c_char_p(b""), C.byref(sub)))
