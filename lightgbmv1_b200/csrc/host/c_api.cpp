@@ -577,6 +577,9 @@ int LGBM_DatasetUpdateParamChecking(const char* old_parameters, const char* new_
   if (a.use_missing != b.use_missing) Log::Fatal("Cannot change use_missing after constructed Dataset handle.");
   if (a.zero_as_missing != b.zero_as_missing) Log::Fatal("Cannot change zero_as_missing after constructed Dataset handle.");
   if (a.enable_bundle != b.enable_bundle) Log::Fatal("Cannot change enable_bundle after constructed Dataset handle.");
+  if (a.data_random_seed != b.data_random_seed) Log::Fatal("Cannot change data_random_seed after constructed Dataset handle.");
+  if (a.max_bin_by_feature != b.max_bin_by_feature) Log::Fatal("Cannot change max_bin_by_feature after constructed Dataset handle.");
+  if (a.categorical_feature != b.categorical_feature) Log::Fatal("Cannot change categorical_feature after constructed Dataset handle.");
   if (a.feature_pre_filter != b.feature_pre_filter) Log::Fatal("Cannot change feature_pre_filter after constructed Dataset handle.");
   if (a.feature_pre_filter && a.min_data_in_leaf < b.min_data_in_leaf)
     Log::Fatal("Reducing `min_data_in_leaf` with `feature_pre_filter=true` may cause unexpected behaviour for features that were pre-filtered by the larger `min_data_in_leaf`.");

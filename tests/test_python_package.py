@@ -203,3 +203,13 @@ def test_dataset_parameter_errors_cpu():
     bad = np.array([3, 2, 1], dtype=np.int32)
     with pytest.raises(capi.LGBMError, match="sorted"):
         ours.check(ours.lib.LGBM_DatasetGetSubset(ds, bad.ctypes.data_as(C.POINTER(C.c_int32)), C.c_int32(3), C.c_char_p(b""), C.byref(sub)))
+
+
+def test_dataset_parameters_cannot_change_after_construction_cpu():
+    ours = capi.ours()
+    ok = lambda old, new: ours.lib.LGBM_DatasetUpdateParamChecking(C.c_char_p(old.encode()), C.c_char_p(new.encode()))
+    assert ok("max_bin=255 categorical_feature=1,2", "num_leaves=63 learning_rate=0.2") == 0
+    for old, new, what in (("max_bin=255", "max_bin=63", "max_bin"), ("categorical_feature=1,2", "categorical_feature=1", "categorical_feature"),
+                           ("max_bin_by_feature=4,8", "max_bin_by_feature=4,9", "max_bin_by_feature"), ("", "zero_as_missing=true", "zero_as_missing")):
+        assert ok(old, new) != 0
+        assert what in ours.lib.LGBM_GetLastError().decode()
